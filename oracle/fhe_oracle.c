@@ -1,0 +1,371 @@
+/*
+ * fhe_oracle.c — CPU restatement of OpenFHE's native DCRTPoly add/mul/NTT path.
+ * TEST INFRASTRUCTURE ONLY (see fhe_oracle.h).  Citations relative to /root/reference.
+ */
+#include "fhe_oracle.h"
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+typedef unsigned __int128 u128;
+
+/* lbcrypto::GetMSB (src/core/include/utils/inttypes / nbtheory): 64 - clz, 0 for 0 */
+uint32_t orc_msb(uint64_t x) { return x ? 64u - (uint32_t)__builtin_clzll(x) : 0u; }
+
+/* ubintnat.h:650-656: mu = floor(2^(2*msb(q)+3) / q) */
+uint64_t orc_compute_mu(uint64_t q) {
+    u128 t = (u128)1 << (2 * orc_msb(q) + 3);
+    return (uint64_t)(t / (u128)q);
+}
+
+/* ubintnat.h:760-767 */
+uint64_t orc_modadd_fast(uint64_t a, uint64_t b, uint64_t q) {
+    uint64_t r = a + b;
+    if (r >= q) r -= q;
+    return r;
+}
+
+/* ubintnat.h:934-938 */
+uint64_t orc_modsub_fast(uint64_t a, uint64_t b, uint64_t q) {
+    if (a < b) return a + q - b;
+    return a - b;
+}
+
+/* ubintnat.h:1398-1413 (generalized Barrett, alpha = n+3); MultD :1919-1932, RShiftD :1901-1903 */
+uint64_t orc_modmul_barrett(uint64_t a, uint64_t b, uint64_t q, uint64_t mu) {
+    u128 prod = (u128)a * b;
+    int64_t n = (int64_t)orc_msb(q) - 2;
+    uint64_t lo = (uint64_t)prod, hi = (uint64_t)(prod >> 64);
+    uint64_t t = (lo >> n) | (hi << (64 - n));      /* RShiftD, truncated to one word */
+    u128 t2 = (u128)t * mu;
+    u128 rv = prod - (u128)q * (t2 >> (n + 7));
+    uint64_t r = (uint64_t)rv;
+    if (r >= q) r -= q;
+    return r;
+}
+
+/* ubintnat.h:1447-1455 */
+uint64_t orc_prep_mulconst(uint64_t w, uint64_t q) { return (uint64_t)(((u128)w << 64) / (u128)q); }
+
+/* ubintnat.h:1491-1497 */
+uint64_t orc_modmul_const(uint64_t a, uint64_t w, uint64_t q, uint64_t wp) {
+    uint64_t qhat = (uint64_t)(((u128)a * wp) >> 64) + 1;
+    int64_t y = (int64_t)(a * w - qhat * q);
+    return (uint64_t)(y >= 0 ? y : y + (int64_t)q);
+}
+
+uint64_t orc_modexp(uint64_t b, uint64_t e, uint64_t q) {
+    uint64_t r = 1 % q;
+    b %= q;
+    while (e) {
+        if (e & 1) r = (uint64_t)(((u128)r * b) % q);
+        b = (uint64_t)(((u128)b * b) % q);
+        e >>= 1;
+    }
+    return r;
+}
+
+/* extended Euclid; q need not be prime (used for 2^-k) */
+uint64_t orc_modinv(uint64_t a, uint64_t q) {
+    __int128 t = 0, nt = 1, r = q, nr = a % q;
+    while (nr != 0) {
+        __int128 qt = r / nr, tmp;
+        tmp = t - qt * nt; t = nt; nt = tmp;
+        tmp = r - qt * nr; r = nr; nr = tmp;
+    }
+    if (t < 0) t += q;
+    return (uint64_t)t;
+}
+
+/* Deterministic Miller-Rabin for 64-bit (bases 2..37): same verdict as the reference's
+ * probabilistic MillerRabinPrimalityTest (nbtheory-impl.h) on true primes/composites. */
+int orc_is_prime(uint64_t p) {
+    static const uint64_t bases[] = {2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 37};
+    if (p < 2) return 0;
+    for (size_t i = 0; i < 12; i++) {
+        if (p == bases[i]) return 1;
+        if (p % bases[i] == 0) return 0;
+    }
+    uint64_t d = p - 1; uint32_t s = 0;
+    while (!(d & 1)) { d >>= 1; s++; }
+    for (size_t i = 0; i < 12; i++) {
+        uint64_t x = orc_modexp(bases[i], d, p);
+        if (x == 1 || x == p - 1) continue;
+        int comp = 1;
+        for (uint32_t r = 1; r < s; r++) {
+            x = (uint64_t)(((u128)x * x) % p);
+            if (x == p - 1) { comp = 0; break; }
+        }
+        if (comp) return 0;
+    }
+    return 1;
+}
+
+/* nbtheory-impl.h:334-359 */
+uint64_t orc_first_prime(uint32_t nbits, uint64_t m) {
+    uint64_t q = (uint64_t)1 << nbits;
+    uint64_t r = q % m;
+    uint64_t q2 = q + 1;
+    if (r > 0) q2 += (m - r);
+    while (!orc_is_prime(q2)) q2 += m;
+    return q2;
+}
+/* nbtheory-impl.h:361-369 */
+uint64_t orc_next_prime(uint64_t q, uint64_t m) {
+    uint64_t c = q + m;
+    while (!orc_is_prime(c)) c += m;
+    return c;
+}
+/* nbtheory-impl.h:372-379 */
+uint64_t orc_previous_prime(uint64_t q, uint64_t m) {
+    uint64_t c = q - m;
+    while (!orc_is_prime(c)) c -= m;
+    return c;
+}
+
+/* nbtheory-impl.h:183-231.  The reference takes a random generator g, r = g^((q-1)/m), then
+ * returns the MINIMUM over all primitive m-th roots (odd powers of r for power-of-two m).
+ * The minimum does not depend on which primitive root one starts from, so any r with
+ * r^(m/2) = -1 reproduces the reference's return value. */
+uint64_t orc_root_of_unity(uint64_t m, uint64_t q) {
+    if ((q - 1) % m != 0) return 0;
+    uint64_t e = (q - 1) / m, r = 0;
+    for (uint64_t g = 2; g < q; g++) {
+        r = orc_modexp(g, e, q);
+        if (orc_modexp(r, m / 2, q) == q - 1) break;
+    }
+    uint64_t r2 = (uint64_t)(((u128)r * r) % q);
+    uint64_t x = r, min = r;
+    for (uint64_t k = 1; k < m; k += 2) {       /* x = r^k over odd k */
+        if (x < min && x != 1) min = x;
+        x = (uint64_t)(((u128)x * r2) % q);
+    }
+    return min;
+}
+
+void orc_gen_dcrt_params(uint32_t nbits, uint32_t N, uint32_t T, uint64_t* q, uint64_t* psi) {
+    uint64_t m = 2ull * N;
+    uint64_t first = orc_first_prime(nbits, m);
+    for (uint32_t i = 0; i < T; i++) {
+        q[i] = orc_previous_prime(i ? q[i - 1] : first, m);
+        psi[i] = orc_root_of_unity(m, q[i]);
+    }
+}
+
+/* ---- one-tower vector ops ---- */
+/* mubintvecnat.h:426-432 / mubintvecnat.cpp:245-264 */
+void orc_vec_modadd(uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t n, uint64_t q) {
+    for (size_t i = 0; i < n; i++) dst[i] = orc_modadd_fast(a[i], b[i], q);
+}
+/* mubintvecnat.cpp:301-307 */
+void orc_vec_modsub(uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t n, uint64_t q) {
+    for (size_t i = 0; i < n; i++) dst[i] = orc_modsub_fast(a[i], b[i], q);
+}
+/* mubintvecnat.h:501-513: mu once per vector, Barrett per element */
+void orc_vec_modmul(uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t n, uint64_t q) {
+    uint64_t mu = orc_compute_mu(q);
+    for (size_t i = 0; i < n; i++) dst[i] = orc_modmul_barrett(a[i], b[i], q, mu);
+}
+/* scalar forms: mubintvecnat.cpp:198-218 (ModAddEq scalar reduces b mod q first), :266-284, :310-332 */
+void orc_vec_modadd_scalar(uint64_t* dst, const uint64_t* a, uint64_t s, size_t n, uint64_t q) {
+    if (s >= q) s %= q;
+    for (size_t i = 0; i < n; i++) dst[i] = orc_modadd_fast(a[i], s, q);
+}
+void orc_vec_modsub_scalar(uint64_t* dst, const uint64_t* a, uint64_t s, size_t n, uint64_t q) {
+    if (s >= q) s %= q;
+    for (size_t i = 0; i < n; i++) dst[i] = orc_modsub_fast(a[i], s, q);
+}
+void orc_vec_modmul_scalar(uint64_t* dst, const uint64_t* a, uint64_t s, size_t n, uint64_t q) {
+    if (s >= q) s %= q;
+    uint64_t mu = orc_compute_mu(q);
+    for (size_t i = 0; i < n; i++) dst[i] = orc_modmul_barrett(a[i], s, q, mu);
+}
+
+/* lbcrypto::ReverseBits(i, msb) */
+static uint32_t bitrev(uint32_t x, uint32_t bits) {
+    uint32_t r = 0;
+    for (uint32_t i = 0; i < bits; i++) { r = (r << 1) | (x & 1); x >>= 1; }
+    return r;
+}
+
+/* transformnat-impl.h:708-763 */
+void orc_precompute(uint64_t psi, uint32_t N, uint64_t q,
+                    uint64_t* W, uint64_t* Wp, uint64_t* WI, uint64_t* WIp,
+                    uint64_t* ninv, uint64_t* ninvp) {
+    uint32_t msb = orc_msb((uint64_t)N - 1);      /* = log2 N */
+    uint64_t mu = orc_compute_mu(q);
+    uint64_t psiinv = orc_modinv(psi, q);
+    uint64_t x = 1, xinv = 1;
+    for (uint32_t i = 0; i < N; i++) {            /* :724-730 */
+        uint32_t r = bitrev(i, msb);
+        W[r] = x; WI[r] = xinv;
+        x = orc_modmul_barrett(x, psi, q, mu);
+        xinv = orc_modmul_barrett(xinv, psiinv, q, mu);
+    }
+    for (uint32_t i = 0; i < N; i++) {            /* :745-750 */
+        Wp[i] = orc_prep_mulconst(W[i], q);
+        WIp[i] = orc_prep_mulconst(WI[i], q);
+    }
+    *ninv = orc_modinv((uint64_t)1 << msb, q);    /* TableCOI[msb], :734-739 */
+    *ninvp = orc_prep_mulconst(*ninv, q);         /* :752-756 */
+}
+
+/* transformnat-impl.h:300-354 (GCC branch): CT, natural in -> bit-reversed out */
+void orc_ntt_fwd(uint64_t* x, uint32_t N, uint64_t q, const uint64_t* W, const uint64_t* Wp) {
+    uint32_t n = N >> 1, t = n, logt = orc_msb(t);
+    for (uint32_t m = 1; m < n; m <<= 1, t >>= 1, --logt) {
+        for (uint32_t i = 0; i < m; ++i) {
+            uint64_t w = W[i + m], wp = Wp[i + m];
+            for (uint32_t j1 = i << logt, j2 = j1 + t; j1 < j2; ++j1) {
+                uint64_t of = orc_modmul_const(x[j1 + t], w, q, wp);
+                uint64_t lo = x[j1];
+                uint64_t hi = lo + of;
+                if (hi >= q) hi -= q;
+                if (lo < of) lo += q;
+                lo -= of;
+                x[j1] = hi; x[j1 + t] = lo;
+            }
+        }
+    }
+    for (uint32_t i = 0; i < (n << 1); i += 2) {  /* peeled t = 1 stage, :332-353 */
+        uint64_t w = W[(i >> 1) + n], wp = Wp[(i >> 1) + n];
+        uint64_t of = orc_modmul_const(x[i + 1], w, q, wp);
+        uint64_t lo = x[i];
+        uint64_t hi = lo + of;
+        if (hi >= q) hi -= q;
+        if (lo < of) lo += q;
+        lo -= of;
+        x[i] = hi; x[i + 1] = lo;
+    }
+}
+
+/* transformnat-impl.h:492-552 (GCC branch): GS, bit-reversed in -> natural out, N^-1 folded in stage 1 */
+void orc_ntt_inv(uint64_t* x, uint32_t N, uint64_t q, const uint64_t* WI, const uint64_t* WIp,
+                 uint64_t ninv, uint64_t ninvp) {
+    uint32_t n = N;
+    for (uint32_t i = 0; i < n; i += 2) {
+        uint64_t w = WI[(i + n) >> 1], wp = WIp[(i + n) >> 1];
+        uint64_t hi = x[i + 1], lo = x[i];
+        uint64_t of = lo;
+        if (of < hi) of += q;
+        of -= hi;
+        lo += hi;
+        if (lo >= q) lo -= q;
+        lo = orc_modmul_const(lo, ninv, q, ninvp);
+        of = orc_modmul_const(of, w, q, wp);
+        of = orc_modmul_const(of, ninv, q, ninvp);
+        x[i] = lo; x[i + 1] = of;
+    }
+    for (uint32_t m = n >> 2, t = 2, logt = 2; m >= 1; m >>= 1, t <<= 1, ++logt) {
+        for (uint32_t i = 0; i < m; ++i) {
+            uint64_t w = WI[i + m], wp = WIp[i + m];
+            for (uint32_t j1 = i << logt, j2 = j1 + t; j1 < j2; ++j1) {
+                uint64_t hi = x[j1 + t], lo = x[j1];
+                uint64_t of = lo;
+                if (of < hi) of += q;
+                of -= hi;
+                lo += hi;
+                if (lo >= q) lo -= q;
+                of = orc_modmul_const(of, w, q, wp);
+                x[j1] = lo; x[j1 + t] = of;
+            }
+        }
+    }
+}
+
+/* ---- DCRTPoly level ---- */
+struct orc_ctx {
+    uint32_t N, T;
+    uint64_t *q, *psi, *ninv, *ninvp;
+    uint64_t *W, *Wp, *WI, *WIp;      /* [T][N] each */
+};
+
+orc_ctx* orc_ctx_create(uint32_t N, uint32_t T, const uint64_t* q, const uint64_t* psi) {
+    orc_ctx* c = (orc_ctx*)calloc(1, sizeof(orc_ctx));
+    c->N = N; c->T = T;
+    c->q = (uint64_t*)malloc(8 * T); c->psi = (uint64_t*)malloc(8 * T);
+    c->ninv = (uint64_t*)malloc(8 * T); c->ninvp = (uint64_t*)malloc(8 * T);
+    size_t tn = (size_t)T * N;
+    c->W = (uint64_t*)malloc(8 * tn); c->Wp = (uint64_t*)malloc(8 * tn);
+    c->WI = (uint64_t*)malloc(8 * tn); c->WIp = (uint64_t*)malloc(8 * tn);
+    memcpy(c->q, q, 8 * T); memcpy(c->psi, psi, 8 * T);
+#pragma omp parallel for schedule(dynamic)
+    for (uint32_t t = 0; t < T; t++)
+        orc_precompute(psi[t], N, q[t], c->W + (size_t)t * N, c->Wp + (size_t)t * N,
+                       c->WI + (size_t)t * N, c->WIp + (size_t)t * N, &c->ninv[t], &c->ninvp[t]);
+    return c;
+}
+
+void orc_ctx_destroy(orc_ctx* c) {
+    if (!c) return;
+    free(c->q); free(c->psi); free(c->ninv); free(c->ninvp);
+    free(c->W); free(c->Wp); free(c->WI); free(c->WIp);
+    free(c);
+}
+
+int orc_max_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+
+/* dcrtpoly.h:142-148,164-200 / dcrtpoly-impl.h:398-416: per tower i, vector op with modulus q_i.
+ * The reference runs `omp parallel for` over towers of ONE poly; here the loop is over all
+ * (batch, tower) units so that nthreads > T can be used for the all-cores CPU figure. */
+void orc_dcrt_elementwise(const orc_ctx* c, int op, uint64_t* dst, const uint64_t* a,
+                          const uint64_t* b, size_t B, int nthreads) {
+    long units = (long)(B * c->T);
+    size_t N = c->N;
+    if (nthreads <= 0) nthreads = orc_max_threads();
+#pragma omp parallel for num_threads(nthreads) schedule(static)
+    for (long u = 0; u < units; u++) {
+        uint64_t q = c->q[u % c->T];
+        size_t off = (size_t)u * N;
+        if (op == 0) orc_vec_modadd(dst + off, a + off, b + off, N, q);
+        else if (op == 1) orc_vec_modsub(dst + off, a + off, b + off, N, q);
+        else orc_vec_modmul(dst + off, a + off, b + off, N, q);
+    }
+}
+
+/* dcrtpoly-impl.h:2518-2524 -> poly-impl.h:412-432 -> transformnat-impl.h:575-602 / 637-666 */
+void orc_dcrt_ntt(const orc_ctx* c, int inverse, uint64_t* x, size_t B, int nthreads) {
+    long units = (long)(B * c->T);
+    size_t N = c->N;
+    if (nthreads <= 0) nthreads = orc_max_threads();
+#pragma omp parallel for num_threads(nthreads) schedule(static)
+    for (long u = 0; u < units; u++) {
+        uint32_t t = (uint32_t)(u % c->T);
+        uint64_t* p = x + (size_t)u * N;
+        if (c->psi[t] == 0 || c->psi[t] == 1) continue;   /* transformnat-impl.h:580-582 */
+        if (!inverse) orc_ntt_fwd(p, c->N, c->q[t], c->W + (size_t)t * N, c->Wp + (size_t)t * N);
+        else orc_ntt_inv(p, c->N, c->q[t], c->WI + (size_t)t * N, c->WIp + (size_t)t * N,
+                         c->ninv[t], c->ninvp[t]);
+    }
+}
+
+/* ---- seeded generator (ours; the reference's Blake2 PRNG is not reproducible) ----
+ * splitmix64 over a counter; rejection-sample the low bitlen(q-1) bits until < q. */
+static inline uint64_t splitmix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+uint64_t orc_uniform_at(uint64_t seed, uint64_t i, uint64_t q) {
+    uint32_t bits = orc_msb(q - 1);
+    uint64_t mask = bits >= 64 ? ~0ull : (((uint64_t)1 << bits) - 1);
+    uint64_t s = splitmix64(seed ^ (i * 0xD1342543DE82EF95ull));
+    for (;;) {
+        s = splitmix64(s);
+        uint64_t v = s & mask;
+        if (v < q) return v;
+    }
+}
+void orc_fill_uniform(uint64_t* x, size_t n, uint64_t q, uint64_t seed, uint64_t first_index) {
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < (long)n; i++) x[i] = orc_uniform_at(seed, first_index + (uint64_t)i, q);
+}

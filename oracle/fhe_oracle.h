@@ -1,0 +1,86 @@
+/*
+ * fhe_oracle.h — CPU restatement of the reference's hot path (TEST INFRASTRUCTURE ONLY).
+ *
+ * This is the parity oracle: plain C (gcc, unsigned __int128) following OpenFHE's
+ * native-integer CPU path function by function.  It is NOT part of the product:
+ * only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+ * legs may load it.  The product (libfhe_b200.so) never links or calls it.
+ *
+ * Parity status: PINNED.  tests/test_oracle_golden.py replays the reference's own
+ * known-answer vectors (UnitTestTransform.cpp:59-98, UnitTestDCRTElements.cpp:285-406,
+ * UnitTestNTT.cpp:53-133, SURVEY §8 N2 parameters) and, in this container,
+ * oracle/_ref/libopenfhe_ref.so (the reference's own sources compiled by
+ * oracle/Makefile) is compared against it on random 60-bit inputs
+ * (tests/test_oracle_vs_ref.py; vectors committed under tests/golden/).
+ *
+ * All citations are relative to /root/reference.
+ */
+#ifndef FHE_ORACLE_H
+#define FHE_ORACLE_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- scalar primitives (src/core/include/math/hal/intnat/ubintnat.h) ---- */
+uint32_t orc_msb(uint64_t x);                                   /* lbcrypto::GetMSB: bit length, 0 for 0 */
+uint64_t orc_compute_mu(uint64_t q);                            /* ubintnat.h:650-656 */
+uint64_t orc_modadd_fast(uint64_t a, uint64_t b, uint64_t q);   /* ubintnat.h:760-767 */
+uint64_t orc_modsub_fast(uint64_t a, uint64_t b, uint64_t q);   /* ubintnat.h:934-938 */
+uint64_t orc_modmul_barrett(uint64_t a, uint64_t b, uint64_t q, uint64_t mu); /* ubintnat.h:1398-1413 */
+uint64_t orc_prep_mulconst(uint64_t w, uint64_t q);             /* ubintnat.h:1447-1455 */
+uint64_t orc_modmul_const(uint64_t a, uint64_t w, uint64_t q, uint64_t wprecon); /* ubintnat.h:1491-1497 */
+uint64_t orc_modexp(uint64_t b, uint64_t e, uint64_t q);
+uint64_t orc_modinv(uint64_t a, uint64_t q);
+
+/* ---- parameter generation (src/core/include/math/nbtheory-impl.h) ---- */
+int      orc_is_prime(uint64_t p);                              /* stands in for MillerRabinPrimalityTest */
+uint64_t orc_first_prime(uint32_t nbits, uint64_t m);           /* nbtheory-impl.h:334-359 */
+uint64_t orc_next_prime(uint64_t q, uint64_t m);                /* nbtheory-impl.h:361-369 */
+uint64_t orc_previous_prime(uint64_t q, uint64_t m);            /* nbtheory-impl.h:372-379 */
+uint64_t orc_root_of_unity(uint64_t m, uint64_t q);             /* nbtheory-impl.h:183-231 (minimum primitive m-th root) */
+/* benchmark/src/poly-benchmark-16k.cpp:82-101: descending PreviousPrime chain + roots */
+void     orc_gen_dcrt_params(uint32_t nbits, uint32_t N, uint32_t T, uint64_t* q, uint64_t* psi);
+
+/* ---- vector ops, one tower (mubintvecnat.h:426-432, 501-513; mubintvecnat.cpp:245-367) ---- */
+void orc_vec_modadd(uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t n, uint64_t q);
+void orc_vec_modsub(uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t n, uint64_t q);
+void orc_vec_modmul(uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t n, uint64_t q);
+void orc_vec_modadd_scalar(uint64_t* dst, const uint64_t* a, uint64_t s, size_t n, uint64_t q);
+void orc_vec_modsub_scalar(uint64_t* dst, const uint64_t* a, uint64_t s, size_t n, uint64_t q);
+void orc_vec_modmul_scalar(uint64_t* dst, const uint64_t* a, uint64_t s, size_t n, uint64_t q);
+
+/* ---- twiddle tables (transformnat-impl.h:708-763) ----
+ * W[bitrev(i)] = psi^i, WI[bitrev(i)] = psi^-i (i < N), Wp/WIp their Shoup companions,
+ * *ninv = N^-1 mod q and *ninvp its companion (TableCOI[log2 N]). */
+void orc_precompute(uint64_t psi, uint32_t N, uint64_t q,
+                    uint64_t* W, uint64_t* Wp, uint64_t* WI, uint64_t* WIp,
+                    uint64_t* ninv, uint64_t* ninvp);
+
+/* ---- NTT kernels, one tower, in place (transformnat-impl.h:300-354, 492-552) ---- */
+void orc_ntt_fwd(uint64_t* x, uint32_t N, uint64_t q, const uint64_t* W, const uint64_t* Wp);
+void orc_ntt_inv(uint64_t* x, uint32_t N, uint64_t q, const uint64_t* WI, const uint64_t* WIp,
+                 uint64_t ninv, uint64_t ninvp);
+
+/* ---- DCRTPoly level: batch x towers, layout [B][T][N] (dcrtpoly.h:142-200,
+ * dcrtpoly-impl.h:410-416, 2518-2524).  op: 0 add, 1 sub, 2 mul.
+ * nthreads: OpenMP threads over the (batch, tower) units; 0 = omp default. ---- */
+typedef struct orc_ctx orc_ctx;
+orc_ctx* orc_ctx_create(uint32_t N, uint32_t T, const uint64_t* q, const uint64_t* psi);
+void     orc_ctx_destroy(orc_ctx* c);
+void     orc_dcrt_elementwise(const orc_ctx* c, int op, uint64_t* dst, const uint64_t* a,
+                              const uint64_t* b, size_t B, int nthreads);
+void     orc_dcrt_ntt(const orc_ctx* c, int inverse, uint64_t* x, size_t B, int nthreads);
+int      orc_max_threads(void);
+
+/* ---- seeded input generator shared with the product's device-side fill
+ * (counter based: value i depends only on (seed, i, q)) ---- */
+uint64_t orc_uniform_at(uint64_t seed, uint64_t i, uint64_t q);
+void     orc_fill_uniform(uint64_t* x, size_t n, uint64_t q, uint64_t seed, uint64_t first_index);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
