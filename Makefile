@@ -1,0 +1,28 @@
+# Builds the product library (hand-written sm_100a kernels + C ABI) in-tree, and the test oracle.
+#   make            -> upmem--openfhe_b200/lib/libfhe_b200.so  and  oracle/libfhe_oracle.so
+#   make ref        -> oracle/_ref/libopenfhe_ref.so (needs /root/reference; this container only)
+NVCC    ?= /usr/local/cuda/bin/nvcc
+PKG     := upmem--openfhe_b200
+CSRC    := $(PKG)/csrc
+LIBDIR  := $(PKG)/lib
+NVFLAGS := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Iinclude -I$(CSRC)
+CU      := $(CSRC)/elementwise.cu $(CSRC)/ntt.cu $(CSRC)/runtime.cu
+OBJ     := $(patsubst $(CSRC)/%.cu,$(LIBDIR)/obj/%.o,$(CU))
+HDR     := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h include/pim/*.h)
+
+.PHONY: all lib oracle ref host clean
+all: lib oracle host
+lib: $(LIBDIR)/libfhe_b200.so
+$(LIBDIR)/obj/%.o: $(CSRC)/%.cu $(HDR)
+	@mkdir -p $(dir $@)
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+$(LIBDIR)/libfhe_b200.so: $(OBJ)
+	$(NVCC) -gencode arch=compute_100a,code=sm_100a -shared -o $@ $^
+oracle:
+	$(MAKE) -C oracle oracle
+ref:
+	$(MAKE) -C oracle ref
+host:
+	@true
+clean:
+	rm -rf $(LIBDIR) && $(MAKE) -C oracle clean

@@ -1,0 +1,161 @@
+/*
+ * fhe_b200.h — C ABI of the B200 backend for the UPMEM--OpenFHE intercept surface.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types.  It replaces what
+ * sat behind the reference's PIM host runtime (all citations relative to the reference tree):
+ *
+ *   reference interface                                         replaced by
+ *   ----------------------------------------------------------  -----------------------------------
+ *   PimManager::getPim / ctor (dpu_alloc, load BOOT)             fhe_init / fhe_shutdown
+ *     src/core/include/pim/PimManager.h:23-29,101-111
+ *   PimManager::allocate / deallocate + DpuMemory                fhe_alloc / fhe_free (device arena)
+ *     src/core/pim/host/PimManager.cpp:56-93, pim/DpuMemory.h:11-82
+ *   PimManager::copy_to_pim / copy_from_pim                      fhe_h2d / fhe_d2h
+ *     src/core/pim/host/PimManager.cpp:5-54
+ *   PimManager::load_kernel + copy_to_pim("meta") + start_kernel fhe_launch (legacy descriptor path)
+ *     pim/PimData.h:275-305,307-329; pim/common.h:9-54; pim/kernel.h:4-8
+ *   PimData operator+ - * / ModAdd ModSub ModMul (+Eq, scalar)   fhe_vec_op / fhe_vec_op_scalar
+ *     pim/PimData.h:46-168
+ *   intended hook NativeVectorT::ModAddEq -> Run_On_Pim          fhe_vec_op
+ *     src/core/lib/math/hal/intnat/mubintvecnat.cpp:250-259
+ *   DCRTPolyImpl::Plus/Minus/Times, += -= *= (OMP over towers)   fhe_dcrt_op (all towers, whole batch,
+ *     lattice/hal/default/dcrtpoly.h:142-200,                       one launch)
+ *     dcrtpoly-impl.h:398-416
+ *   DCRTPolyImpl::SwitchFormat -> ChineseRemainderTransformFTT   fhe_ntt_forward / fhe_ntt_inverse
+ *     dcrtpoly-impl.h:2518-2524, poly-impl.h:412-432,
+ *     math/hal/intnat/transformnat-impl.h:575-602,637-666
+ *   ChineseRemainderTransformFTTNat::PreCompute (twiddle cache)  fhe_ring_create
+ *     transformnat-impl.h:708-763
+ *   FirstPrime / PreviousPrime / RootOfUnity parameter recipe    fhe_gen_params (host side, setup only)
+ *     math/nbtheory-impl.h:183-231,334-379;
+ *     benchmark/src/poly-benchmark-16k.cpp:82-101
+ *
+ * Conventions
+ *   - Every function returns 0 on success, a negative FHE_E* code on failure; the message is in
+ *     fhe_last_error() (thread local).  There is NO CPU fallback: without a CUDA device fhe_init
+ *     fails and nothing else can be called.
+ *   - Device buffers are plain device addresses carried as uint64_t (fhe_dptr), so a caller may
+ *     also pass memory it allocated itself (cudaMalloc, torch).
+ *   - Polynomial data layout: [batch][tower][N] uint64, coefficients contiguous per tower (the
+ *     reference's DCRTPoly layout, towers of one polynomial adjacent).  Coefficients must be
+ *     < q_tower (the reference's *Fast* precondition, ubintnat.h:740-745).
+ *   - `stream` is an index into the context's stream pool (0 <= stream < fhe_num_streams), or
+ *     FHE_STREAM_LEGACY (-1) for the CUDA legacy default stream.  Launches are asynchronous;
+ *     fhe_sync waits.  Calls on different buffers may be issued concurrently from several
+ *     threads (the reference's callers are OpenMP loops over towers, dcrtpoly-impl.h:412).
+ */
+#ifndef FHE_B200_H
+#define FHE_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fhe_ctx fhe_ctx;     /* one CUDA device: streams, arena, pinned staging */
+typedef struct fhe_ring fhe_ring;   /* (N, towers, q_i, psi_i) + device-resident constant tables */
+typedef uint64_t fhe_dptr;          /* device address */
+
+enum {
+    FHE_OK = 0,
+    FHE_EINVAL = -1,      /* bad argument */
+    FHE_ECUDA = -2,       /* CUDA runtime error (message has the CUDA string) */
+    FHE_ENOMEM = -3,      /* device arena exhausted */
+    FHE_ENODEV = -4,      /* no usable CUDA device: there is no CPU fallback */
+    FHE_EUNSUPPORTED = -5 /* valid request this build does not implement */
+};
+
+enum { FHE_OP_ADD = 0, FHE_OP_SUB = 1, FHE_OP_MUL = 2 };
+enum { FHE_STREAM_LEGACY = -1 };
+
+/* Kernel ids of the legacy descriptor path: the five binaries named in pim/kernel.h:4-8. */
+enum { FHE_KERNEL_BOOT = 0, FHE_KERNEL_MOD_ADD = 1, FHE_KERNEL_MOD_MULT = 2, FHE_KERNEL_MOD_SUB = 3,
+       FHE_KERNEL_MOD_OPS = 4 };
+
+/* ---- runtime ------------------------------------------------------------------------------ */
+const char* fhe_last_error(void);
+const char* fhe_version(void);
+/* opts: "key=value,..."; keys: streams (default 4), arena_mb (initial arena slab, default 256),
+ * staging_mb (pinned staging per direction for the *_host calls, default 64). */
+int fhe_init(int device, const char* opts, fhe_ctx** out);
+int fhe_shutdown(fhe_ctx* ctx);
+int fhe_device(const fhe_ctx* ctx);
+int fhe_num_streams(const fhe_ctx* ctx);
+int fhe_sync(fhe_ctx* ctx, int stream);               /* stream = -2: whole device */
+/* number of kernels this library has launched since it was loaded */
+long fhe_launch_count(void);
+
+/* ---- memory ------------------------------------------------------------------------------- */
+int fhe_alloc(fhe_ctx* ctx, size_t bytes, fhe_dptr* out);        /* 256-byte aligned */
+int fhe_free(fhe_ctx* ctx, fhe_dptr p);
+int fhe_arena_stats(fhe_ctx* ctx, size_t* reserved_bytes, size_t* in_use_bytes);
+int fhe_host_alloc(fhe_ctx* ctx, size_t bytes, void** out);      /* pinned host memory */
+int fhe_host_free(fhe_ctx* ctx, void* p);
+int fhe_h2d(fhe_ctx* ctx, fhe_dptr dst, const void* src, size_t bytes, int stream);
+int fhe_d2h(fhe_ctx* ctx, void* dst, fhe_dptr src, size_t bytes, int stream);
+int fhe_d2d(fhe_ctx* ctx, fhe_dptr dst, fhe_dptr src, size_t bytes, int stream);
+
+/* ---- timing on the launching stream (CUDA events) ------------------------------------------ */
+int fhe_timer_start(fhe_ctx* ctx, int stream);
+int fhe_timer_stop(fhe_ctx* ctx, int stream, float* elapsed_ms);  /* waits for the stop event */
+
+/* ---- parameters (host, setup) --------------------------------------------------------------- */
+/* q_0 = PreviousPrime(FirstPrime(nbits, 2N), 2N), q_i = PreviousPrime(q_{i-1}, 2N),
+ * psi_i = minimum primitive 2N-th root of unity mod q_i. */
+int fhe_gen_params(uint32_t nbits, uint32_t N, uint32_t towers, uint64_t* q, uint64_t* psi);
+uint64_t fhe_root_of_unity(uint64_t m, uint64_t q);              /* 0 if m does not divide q-1 */
+
+/* ---- ring --------------------------------------------------------------------------------- */
+/* N power of two, 1 <= N <= 65536; 4 <= q_i < 2^61; psi_i a primitive 2N-th root mod q_i
+ * (psi may be NULL when only fhe_dcrt_op is needed).  Builds the Barrett constants and, per
+ * tower, the four tables PreCompute builds, and keeps them in HBM. */
+int fhe_ring_create(fhe_ctx* ctx, uint32_t N, uint32_t towers, const uint64_t* q,
+                    const uint64_t* psi, fhe_ring** out);
+int fhe_ring_destroy(fhe_ring* ring);
+uint32_t fhe_ring_n(const fhe_ring* ring);
+uint32_t fhe_ring_towers(const fhe_ring* ring);
+/* copies table `which` (0 W, 1 W companion, 2 W^-1, 3 W^-1 companion; N words) of one tower to host */
+int fhe_ring_table(const fhe_ring* ring, uint32_t tower, int which, uint64_t* out);
+
+/* ---- the hot path: device-resident operands -------------------------------------------------- */
+/* dst = a (op) b for every tower of every polynomial of the batch; dst may alias a or b. */
+int fhe_dcrt_op(fhe_ring* ring, int op, fhe_dptr dst, fhe_dptr a, fhe_dptr b, size_t batch, int stream);
+/* in-place COEFFICIENT -> EVALUATION (bit-reversed order), and back */
+int fhe_ntt_forward(fhe_ring* ring, fhe_dptr x, size_t batch, int stream);
+int fhe_ntt_inverse(fhe_ring* ring, fhe_dptr x, size_t batch, int stream);
+/* same, selecting the kernel family: 0 auto, 1 single-CTA shared-memory kernel (N <= 4096) */
+int fhe_ntt_algo(fhe_ring* ring, fhe_dptr x, size_t batch, int inverse, int algo, int stream);
+/* c = INTT(NTT(a) .* NTT(b)): negacyclic product of COEFFICIENT-format polynomials; a and b are
+ * left in EVALUATION format (they are transformed in place), c may alias neither. */
+int fhe_poly_mul(fhe_ring* ring, fhe_dptr c, fhe_dptr a, fhe_dptr b, size_t batch, int stream);
+/* seeded uniform coefficients in [0, q_tower) (synthetic inputs for tests and benchmarks) */
+int fhe_fill_uniform(fhe_ring* ring, fhe_dptr dst, size_t batch, uint64_t seed, int stream);
+
+/* ---- flat vectors with an explicit modulus (the PimData surface) ----------------------------- */
+int fhe_vec_op(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, fhe_dptr b, size_t n, uint64_t q, int stream);
+int fhe_vec_op_scalar(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, uint64_t scalar, size_t n,
+                      uint64_t q, int stream);
+
+/* ---- legacy descriptor path ------------------------------------------------------------------ */
+/* desc points to a `struct mod_add_sub_mult` (pim/common.h:23-30) whose operands are byte offsets
+ * from `heap_base` and byte sizes; kernel_id picks add / sub / mult.  Blocking, like
+ * PimManager::start_kernel (DPU_SYNCHRONOUS, PimManager.h:68). */
+int fhe_launch(fhe_ctx* ctx, int kernel_id, const void* desc, fhe_dptr heap_base);
+
+/* ---- end-to-end convenience: HOST operands -------------------------------------------------- */
+/* dst = a (op) b with host buffers of batch*towers*N words each.  Streams the batch through the
+ * device in chunks: pinned staging, H2D / kernel / D2H overlapped on separate streams. Blocking. */
+int fhe_dcrt_op_host(fhe_ring* ring, int op, uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t batch);
+/* in-place transform of a host buffer (inverse = 0 forward, 1 inverse). Blocking. */
+int fhe_ntt_host(fhe_ring* ring, uint64_t* x, size_t batch, int inverse);
+
+/* ---- diagnostics ---------------------------------------------------------------------------- */
+/* integer-pipe probe: launches blocks x threads, each thread doing iters x 8 (mulhi64 + mullo64);
+ * returns the kernel time so the caller can derive 64-bit multiply throughput. */
+int fhe_imad_probe(fhe_ctx* ctx, int blocks, int threads, int iters, float* elapsed_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FHE_B200_H */

@@ -1,0 +1,134 @@
+"""ctypes wrapper of the CPU oracle (oracle/fhe_oracle.c).  TEST INFRASTRUCTURE ONLY."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_SO = os.path.join(ROOT, "oracle", "libfhe_oracle.so")
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libopenfhe_ref.so")
+
+u64, u32, vp, sz, ci = ctypes.c_uint64, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int
+
+
+def _p(a):
+    return a.ctypes.data_as(vp)
+
+
+class Oracle:
+    def __init__(self, lib):
+        L = self.L = lib
+        for name, res, args in [
+            ("orc_msb", u32, [u64]), ("orc_compute_mu", u64, [u64]),
+            ("orc_modadd_fast", u64, [u64, u64, u64]), ("orc_modsub_fast", u64, [u64, u64, u64]),
+            ("orc_modmul_barrett", u64, [u64, u64, u64, u64]), ("orc_prep_mulconst", u64, [u64, u64]),
+            ("orc_modmul_const", u64, [u64, u64, u64, u64]), ("orc_modexp", u64, [u64, u64, u64]),
+            ("orc_modinv", u64, [u64, u64]), ("orc_is_prime", ci, [u64]),
+            ("orc_first_prime", u64, [u32, u64]), ("orc_next_prime", u64, [u64, u64]),
+            ("orc_previous_prime", u64, [u64, u64]), ("orc_root_of_unity", u64, [u64, u64]),
+            ("orc_gen_dcrt_params", None, [u32, u32, u32, vp, vp]),
+            ("orc_vec_modadd", None, [vp, vp, vp, sz, u64]), ("orc_vec_modsub", None, [vp, vp, vp, sz, u64]),
+            ("orc_vec_modmul", None, [vp, vp, vp, sz, u64]),
+            ("orc_vec_modadd_scalar", None, [vp, vp, u64, sz, u64]),
+            ("orc_vec_modsub_scalar", None, [vp, vp, u64, sz, u64]),
+            ("orc_vec_modmul_scalar", None, [vp, vp, u64, sz, u64]),
+            ("orc_precompute", None, [u64, u32, u64, vp, vp, vp, vp, vp, vp]),
+            ("orc_ntt_fwd", None, [vp, u32, u64, vp, vp]),
+            ("orc_ntt_inv", None, [vp, u32, u64, vp, vp, u64, u64]),
+            ("orc_ctx_create", vp, [u32, u32, vp, vp]), ("orc_ctx_destroy", None, [vp]),
+            ("orc_dcrt_elementwise", None, [vp, ci, vp, vp, vp, sz, ci]),
+            ("orc_dcrt_ntt", None, [vp, ci, vp, sz, ci]), ("orc_max_threads", ci, []),
+            ("orc_uniform_at", u64, [u64, u64, u64]), ("orc_fill_uniform", None, [vp, sz, u64, u64, u64]),
+        ]:
+            f = getattr(L, name)
+            f.restype, f.argtypes = res, args
+
+    def gen_params(self, nbits, n, towers):
+        q = np.zeros(towers, np.uint64)
+        psi = np.zeros(towers, np.uint64)
+        self.L.orc_gen_dcrt_params(nbits, n, towers, _p(q), _p(psi))
+        return q, psi
+
+    def precompute(self, psi, n, q):
+        W, Wp, WI, WIp = (np.zeros(n, np.uint64) for _ in range(4))
+        ni, nip = u64(), u64()
+        self.L.orc_precompute(int(psi), n, int(q), _p(W), _p(Wp), _p(WI), _p(WIp), ctypes.byref(ni), ctypes.byref(nip))
+        return W, Wp, WI, WIp, ni.value, nip.value
+
+    def ntt_fwd(self, x, q, psi):
+        x = np.array(x, dtype=np.uint64)
+        W, Wp, _, _, _, _ = self.precompute(psi, len(x), q)
+        self.L.orc_ntt_fwd(_p(x), len(x), int(q), _p(W), _p(Wp))
+        return x
+
+    def ntt_inv(self, x, q, psi):
+        x = np.array(x, dtype=np.uint64)
+        _, _, WI, WIp, ni, nip = self.precompute(psi, len(x), q)
+        self.L.orc_ntt_inv(_p(x), len(x), int(q), _p(WI), _p(WIp), ni, nip)
+        return x
+
+    def vec(self, op, a, b, q):
+        a = np.ascontiguousarray(a, np.uint64)
+        b = np.ascontiguousarray(b, np.uint64)
+        out = np.empty_like(a)
+        f = [self.L.orc_vec_modadd, self.L.orc_vec_modsub, self.L.orc_vec_modmul][op]
+        f(_p(out), _p(a), _p(b), a.size, int(q))
+        return out
+
+    def vec_scalar(self, op, a, s, q):
+        a = np.ascontiguousarray(a, np.uint64)
+        out = np.empty_like(a)
+        f = [self.L.orc_vec_modadd_scalar, self.L.orc_vec_modsub_scalar, self.L.orc_vec_modmul_scalar][op]
+        f(_p(out), _p(a), int(s), a.size, int(q))
+        return out
+
+    def ctx(self, n, q, psi):
+        return OracleCtx(self, n, q, psi)
+
+    def fill_uniform(self, n, q, seed, first=0):
+        x = np.empty(n, np.uint64)
+        self.L.orc_fill_uniform(_p(x), n, int(q), int(seed), int(first))
+        return x
+
+    def fill_ring(self, batch, n, q, seed):
+        """Same values as fhe_fill_uniform: flat index over [batch][tower][N]."""
+        T = len(q)
+        out = np.empty((batch, T, n), np.uint64)
+        for b in range(batch):
+            for t in range(T):
+                out[b, t] = self.fill_uniform(n, q[t], seed, (b * T + t) * n)
+        return out
+
+
+class OracleCtx:
+    def __init__(self, o, n, q, psi):
+        self.o, self.n = o, n
+        self.q = np.ascontiguousarray(q, np.uint64)
+        self.psi = np.ascontiguousarray(psi, np.uint64)
+        self.h = o.L.orc_ctx_create(n, len(self.q), _p(self.q), _p(self.psi))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.o.L.orc_ctx_destroy(self.h)
+            self.h = None
+
+    def elementwise(self, op, a, b, threads=0):
+        a = np.ascontiguousarray(a, np.uint64)
+        b = np.ascontiguousarray(b, np.uint64)
+        out = np.empty_like(a)
+        batch = a.size // (len(self.q) * self.n)
+        self.o.L.orc_dcrt_elementwise(self.h, op, _p(out), _p(a), _p(b), batch, threads)
+        return out
+
+    def ntt(self, x, inverse=False, threads=0):
+        x = np.array(x, dtype=np.uint64, copy=True)
+        batch = x.size // (len(self.q) * self.n)
+        self.o.L.orc_dcrt_ntt(self.h, 1 if inverse else 0, _p(x), batch, threads)
+        return x
+
+
+def load():
+    if not os.path.exists(ORACLE_SO):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "oracle"])
+    return Oracle(ctypes.CDLL(ORACLE_SO))

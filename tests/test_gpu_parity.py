@@ -1,0 +1,235 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the CPU oracle — bit exact.
+
+Shapes follow the reference's own tests (tiny rings with fixed vectors) and
+BASELINE.json's configs (N = 2^14..2^16 with 60-bit moduli) at batch sizes the oracle finishes in
+seconds; full-size configs are covered by size-independent properties in test_gpu_properties.py.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ADD, SUB, MUL = 0, 1, 2
+
+
+def rand_polys(rng, batch, n, q):
+    return np.stack([rng.integers(0, int(qt), size=(batch, n), dtype=np.uint64) for qt in q], axis=1)
+
+
+def params(oracle, nbits, n, towers):
+    return oracle.gen_params(nbits, n, towers)
+
+
+# ---- reference KATs replayed on the GPU --------------------------------------------------------
+def test_kat_crt_polynomial_mult(pkg, backend):
+    """UnitTestTransform.cpp:59-98: q=113, N=4, a=b=[1,2,4,1] -> [94,109,11,18]."""
+    ring = pkg.Ring(backend, 4, [113], [18])
+    a = pkg.DCRTPolyBatch(ring, 1, pkg.COEFFICIENT, np.array([1, 2, 4, 1], np.uint64))
+    b = a.clone()
+    a.SwitchFormat()
+    assert a.to_host().reshape(-1).tolist() == [46, 62, 104, 18]
+    b.SwitchFormat()
+    c = a * b
+    c.SwitchFormat()
+    assert c.to_host().reshape(-1).tolist() == [94, 109, 11, 18]
+    ring.close()
+
+
+def test_kat_dcrt_arithmetic(pkg, backend):
+    """UnitTestDCRTElements.cpp:285-406: 3 towers {8353,8369,8513}, N=4."""
+    q = [8353, 8369, 8513]
+    ring = pkg.Ring(backend, 4, q)
+    a = pkg.DCRTPolyBatch(ring, 1, pkg.EVALUATION, np.tile(np.array([2, 4, 3, 2], np.uint64), 3))
+    b = pkg.DCRTPolyBatch(ring, 1, pkg.EVALUATION, np.tile(np.array([2, 1, 2, 0], np.uint64), 3))
+    for res, exp in [(a + b, [4, 5, 5, 2]), (a - b, [0, 3, 1, 2]), (a * b, [4, 4, 6, 0])]:
+        assert res.to_host().reshape(3, 4).tolist() == [exp] * 3
+    c = a.clone(); c += b
+    assert c.to_host().reshape(3, 4).tolist() == [[4, 5, 5, 2]] * 3
+    c = a.clone(); c -= b
+    assert c.to_host().reshape(3, 4).tolist() == [[0, 3, 1, 2]] * 3
+    c = a.clone(); c *= b
+    assert c.to_host().reshape(3, 4).tolist() == [[4, 4, 6, 0]] * 3
+    ring.close()
+
+
+def test_times_requires_evaluation(pkg, backend):
+    """dcrtpoly.h:188-189: Times throws outside EVALUATION format."""
+    ring = pkg.Ring(backend, 4, [113], [18])
+    a = pkg.DCRTPolyBatch(ring, 1, pkg.COEFFICIENT, np.array([1, 2, 4, 1], np.uint64))
+    with pytest.raises(RuntimeError):
+        a.Times(a)
+    ring.close()
+
+
+# ---- element-wise ops --------------------------------------------------------------------------
+@pytest.mark.parametrize("n,towers,batch,nbits", [
+    (4, 3, 1, 14), (8, 2, 5, 28), (2, 1, 1, 20), (1024, 3, 2, 60), (2048, 2, 3, 60),
+    (1 << 14, 2, 2, 60), (1 << 14, 8, 4, 60), (1 << 15, 4, 1, 59), (1 << 16, 3, 2, 60), (1 << 12, 5, 7, 50),
+])
+def test_elementwise_vs_oracle(pkg, backend, oracle, n, towers, batch, nbits):
+    q, psi = params(oracle, nbits, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q)
+    rng = np.random.default_rng(1000 + n + towers)
+    a, b = rand_polys(rng, batch, n, q), rand_polys(rng, batch, n, q)
+    # edge vectors: zeros, q-1, alternating
+    a[0, :, : min(n, 8)] = 0
+    b[0, :, : min(n, 8)] = (q - 1)[:, None]
+    a[-1, :, -min(n, 8):] = (q - 1)[:, None]
+    b[-1, :, -min(n, 8):] = (q - 1)[:, None]
+    da = pkg.DCRTPolyBatch(ring, batch, pkg.EVALUATION, a)
+    db = pkg.DCRTPolyBatch(ring, batch, pkg.EVALUATION, b)
+    for op, res in [(ADD, da + db), (SUB, da - db), (MUL, da * db)]:
+        exp = octx.elementwise(op, a, b)
+        assert np.array_equal(res.to_host(), exp), f"op {op}"
+    for op in (ADD, SUB, MUL):                       # in-place forms
+        c = da.clone()
+        if op == ADD: c += db
+        elif op == SUB: c -= db
+        else: c *= db
+        assert np.array_equal(c.to_host(), octx.elementwise(op, a, b))
+    ring.close()
+
+
+# ---- tables ------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,nbits", [(4, 10), (256, 30), (1 << 12, 60), (1 << 16, 60)])
+def test_twiddle_tables_vs_oracle(pkg, backend, oracle, n, nbits):
+    q, psi = params(oracle, nbits, n, 2)
+    ring = pkg.Ring(backend, n, q, psi)
+    for t in range(2):
+        W, Wp, WI, WIp, _, _ = oracle.precompute(psi[t], n, q[t])
+        for which, exp in enumerate([W, Wp, WI, WIp]):
+            assert np.array_equal(ring.table(t, which), exp)
+    ring.close()
+
+
+# ---- NTT ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize("logn,towers,batch,nbits", [
+    (1, 1, 1, 10), (2, 2, 3, 12), (3, 2, 1, 22), (5, 1, 2, 30), (8, 3, 2, 60),
+    (9, 2, 3, 60), (10, 1, 1, 60), (11, 3, 17, 55), (12, 2, 16, 60), (13, 2, 5, 60),
+    (14, 2, 2, 60), (14, 4, 33, 60), (15, 3, 4, 60), (16, 2, 3, 60), (16, 3, 16, 60), (16, 1, 1, 60),
+])
+def test_ntt_vs_oracle(pkg, backend, oracle, logn, towers, batch, nbits):
+    n = 1 << logn
+    q, psi = params(oracle, nbits, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q, psi)
+    rng = np.random.default_rng(7 + logn * 31 + batch)
+    x = rand_polys(rng, batch, n, q)
+    x[0, :, 0] = (q - 1)
+    x[-1, :, -1] = 0
+    d = pkg.DCRTPolyBatch(ring, batch, pkg.COEFFICIENT, x)
+    d.SwitchFormat()
+    fwd = d.to_host()
+    exp = octx.ntt(x, inverse=False)
+    assert np.array_equal(fwd, exp), "forward"
+    d.SwitchFormat()
+    assert np.array_equal(d.to_host(), x), "round trip"
+    # inverse on its own, from arbitrary evaluation-domain data
+    y = rand_polys(rng, batch, n, q)
+    e = pkg.DCRTPolyBatch(ring, batch, pkg.EVALUATION, y)
+    e.SwitchFormat()
+    assert np.array_equal(e.to_host(), octx.ntt(y, inverse=True)), "inverse"
+    ring.close()
+
+
+@pytest.mark.parametrize("logn", [9, 10, 12])
+def test_ntt_small_kernel_matches_two_pass(pkg, backend, oracle, logn):
+    n = 1 << logn
+    q, psi = params(oracle, 60, n, 2)
+    ring = pkg.Ring(backend, n, q, psi)
+    x = rand_polys(np.random.default_rng(3), 3, n, q)
+    d1 = pkg.DCRTPolyBatch(ring, 3, pkg.COEFFICIENT, x)
+    d2 = d1.clone()
+    ring.ntt(d1.dptr, 3, inverse=False, algo=0)
+    ring.ntt(d2.dptr, 3, inverse=False, algo=1)
+    assert np.array_equal(d1.to_host(), d2.to_host())
+    ring.ntt(d1.dptr, 3, inverse=True, algo=1)
+    ring.ntt(d2.dptr, 3, inverse=True, algo=0)
+    assert np.array_equal(d1.to_host(), x) and np.array_equal(d2.to_host(), x)
+    ring.close()
+
+
+def test_trivial_root_is_identity(pkg, backend):
+    """transformnat-impl.h:580-582: psi in {0,1} leaves the element untouched."""
+    ring = pkg.Ring(backend, 8, [113, 97], [1, 0])
+    x = np.arange(16, dtype=np.uint64)
+    d = pkg.DCRTPolyBatch(ring, 1, pkg.COEFFICIENT, x)
+    d.SwitchFormat()
+    assert np.array_equal(d.to_host().reshape(-1), x)
+    ring.close()
+
+
+def test_poly_mul_is_negacyclic_convolution(pkg, backend, oracle):
+    n, towers = 64, 2
+    q, psi = params(oracle, 40, n, towers)
+    ring = pkg.Ring(backend, n, q, psi)
+    rng = np.random.default_rng(11)
+    a, b = rand_polys(rng, 2, n, q), rand_polys(rng, 2, n, q)
+    da = pkg.DCRTPolyBatch(ring, 2, pkg.COEFFICIENT, a)
+    db = pkg.DCRTPolyBatch(ring, 2, pkg.COEFFICIENT, b)
+    dc = pkg.DCRTPolyBatch(ring, 2, pkg.COEFFICIENT)
+    ring.poly_mul(dc.dptr, da.dptr, db.dptr, 2)
+    got = dc.to_host()
+    for bi in range(2):
+        for t in range(towers):
+            qq = int(q[t])
+            exp = [0] * n
+            for i in range(n):
+                for j in range(n):
+                    k, v = i + j, int(a[bi, t, i]) * int(b[bi, t, j])
+                    if k >= n: exp[k - n] = (exp[k - n] - v) % qq
+                    else: exp[k] = (exp[k] + v) % qq
+            assert got[bi, t].tolist() == exp
+    ring.close()
+
+
+# ---- flat vectors (PimData surface) --------------------------------------------------------------
+@pytest.mark.parametrize("n", [1, 2, 3, 255, 1024, 4097, 100001])
+@pytest.mark.parametrize("q", [73, 8353, 1152921504606748673])
+def test_vec_ops_vs_oracle(pkg, backend, oracle, n, q):
+    rng = np.random.default_rng(n)
+    a = rng.integers(0, q, size=n, dtype=np.uint64)
+    b = rng.integers(0, q, size=n, dtype=np.uint64)
+    da, db, dd = backend.alloc(n * 8), backend.alloc(n * 8), backend.alloc(n * 8)
+    backend.h2d(da, a); backend.h2d(db, b)
+    for op in (ADD, SUB, MUL):
+        backend.vec_op(op, dd, da, db, n, q)
+        assert np.array_equal(backend.d2h(dd, n), oracle.vec(op, a, b, q))
+        s = int(rng.integers(0, 2**63))
+        backend.vec_op_scalar(op, dd, da, s, n, q)
+        assert np.array_equal(backend.d2h(dd, n), oracle.vec_scalar(op, a, s, q))
+    for p in (da, db, dd):
+        backend.free(p)
+
+
+# ---- host-operand (end-to-end) entry points -------------------------------------------------------
+def test_host_pipeline_vs_oracle(pkg, backend, oracle):
+    n, towers, batch = 1 << 14, 4, 80           # 80 items of 512 KB -> several 32 MB chunks
+    q, psi = params(oracle, 60, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q, psi)
+    rng = np.random.default_rng(5)
+    a, b = rand_polys(rng, batch, n, q), rand_polys(rng, batch, n, q)
+    out = np.empty_like(a)
+    for op in (ADD, MUL):
+        ring.op_host(op, out, a, b, batch)
+        assert np.array_equal(out, octx.elementwise(op, a, b))
+    x = a.copy()
+    ring.ntt_host(x, batch, inverse=False)
+    assert np.array_equal(x, octx.ntt(a, inverse=False))
+    ring.ntt_host(x, batch, inverse=True)
+    assert np.array_equal(x, a)
+    ring.close()
+
+
+def test_fill_uniform_matches_oracle_generator(pkg, backend, oracle):
+    n, towers, batch = 1 << 10, 3, 4
+    q, psi = params(oracle, 60, n, towers)
+    ring = pkg.Ring(backend, n, q)
+    d = pkg.DCRTPolyBatch(ring, batch)
+    ring.fill_uniform(d.dptr, batch, 20260001)
+    got = d.to_host()
+    assert np.array_equal(got, oracle.fill_ring(batch, n, q, 20260001))
+    assert (got < q[None, :, None]).all()
+    ring.close()

@@ -1,0 +1,14 @@
+"""B200 backend for the UPMEM--OpenFHE intercept surface: tower-wise modular add / sub / mul of RNS
+polynomials in the evaluation domain and the forward / inverse negacyclic NTT, as hand-written
+sm_100a kernels behind a C ABI (include/fhe_b200.h).
+
+The directory name is not a Python identifier; import it with
+    importlib.import_module("upmem--openfhe_b200")
+Importing fails if lib/libfhe_b200.so has not been built: there is no CPU fallback.
+"""
+from . import _native
+from ._native import FheError, LIB_PATH, OP_ADD, OP_MUL, OP_SUB, SIGNATURES
+from .dcrtpoly import COEFFICIENT, EVALUATION, Backend, DCRTPolyBatch, Ring, gen_params
+
+__all__ = ["Backend", "Ring", "DCRTPolyBatch", "gen_params", "FheError", "EVALUATION", "COEFFICIENT",
+           "OP_ADD", "OP_SUB", "OP_MUL", "LIB_PATH", "SIGNATURES"]

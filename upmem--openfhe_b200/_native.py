@@ -1,0 +1,89 @@
+"""ctypes binding of the C ABI declared in include/fhe_b200.h.
+
+This is the reference-side binding a maintainer would add for a Python caller; the C++ binding is
+include/pim/*.h.  There is no fallback: if the CUDA library is missing, importing fails loudly, and
+if no B200 is visible every compute call fails with FHE_ENODEV.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libfhe_b200.so")
+
+u64 = ctypes.c_uint64
+u32 = ctypes.c_uint32
+vp = ctypes.c_void_p
+sz = ctypes.c_size_t
+ci = ctypes.c_int
+pu64 = ctypes.POINTER(ctypes.c_uint64)
+
+# name -> (restype, argtypes): exactly the symbols include/fhe_b200.h declares
+SIGNATURES = {
+    "fhe_last_error": (ctypes.c_char_p, []),
+    "fhe_version": (ctypes.c_char_p, []),
+    "fhe_init": (ci, [ci, ctypes.c_char_p, ctypes.POINTER(vp)]),
+    "fhe_shutdown": (ci, [vp]),
+    "fhe_device": (ci, [vp]),
+    "fhe_num_streams": (ci, [vp]),
+    "fhe_sync": (ci, [vp, ci]),
+    "fhe_launch_count": (ctypes.c_long, []),
+    "fhe_alloc": (ci, [vp, sz, ctypes.POINTER(u64)]),
+    "fhe_free": (ci, [vp, u64]),
+    "fhe_arena_stats": (ci, [vp, ctypes.POINTER(sz), ctypes.POINTER(sz)]),
+    "fhe_host_alloc": (ci, [vp, sz, ctypes.POINTER(vp)]),
+    "fhe_host_free": (ci, [vp, vp]),
+    "fhe_h2d": (ci, [vp, u64, vp, sz, ci]),
+    "fhe_d2h": (ci, [vp, vp, u64, sz, ci]),
+    "fhe_d2d": (ci, [vp, u64, u64, sz, ci]),
+    "fhe_timer_start": (ci, [vp, ci]),
+    "fhe_timer_stop": (ci, [vp, ci, ctypes.POINTER(ctypes.c_float)]),
+    "fhe_gen_params": (ci, [u32, u32, u32, vp, vp]),
+    "fhe_root_of_unity": (u64, [u64, u64]),
+    "fhe_ring_create": (ci, [vp, u32, u32, vp, vp, ctypes.POINTER(vp)]),
+    "fhe_ring_destroy": (ci, [vp]),
+    "fhe_ring_n": (u32, [vp]),
+    "fhe_ring_towers": (u32, [vp]),
+    "fhe_ring_table": (ci, [vp, u32, ci, vp]),
+    "fhe_dcrt_op": (ci, [vp, ci, u64, u64, u64, sz, ci]),
+    "fhe_ntt_forward": (ci, [vp, u64, sz, ci]),
+    "fhe_ntt_inverse": (ci, [vp, u64, sz, ci]),
+    "fhe_ntt_algo": (ci, [vp, u64, sz, ci, ci, ci]),
+    "fhe_poly_mul": (ci, [vp, u64, u64, u64, sz, ci]),
+    "fhe_fill_uniform": (ci, [vp, u64, sz, u64, ci]),
+    "fhe_vec_op": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),
+    "fhe_vec_op_scalar": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),
+    "fhe_launch": (ci, [vp, ci, vp, u64]),
+    "fhe_dcrt_op_host": (ci, [vp, ci, vp, vp, vp, sz]),
+    "fhe_ntt_host": (ci, [vp, vp, sz, ci]),
+    "fhe_imad_probe": (ci, [vp, ci, ci, ci, ctypes.POINTER(ctypes.c_float)]),
+}
+
+FHE_OK, FHE_EINVAL, FHE_ECUDA, FHE_ENOMEM, FHE_ENODEV, FHE_EUNSUPPORTED = 0, -1, -2, -3, -4, -5
+OP_ADD, OP_SUB, OP_MUL = 0, 1, 2
+
+
+class FheError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"fhe_b200 error {code}: {msg}")
+        self.code = code
+
+
+def load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `make lib` (or __graft_entry__.build()). "
+            "This backend has no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if the library does not export it
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+lib = load()
+
+
+def check(rc):
+    if rc != 0:
+        raise FheError(rc, lib.fhe_last_error().decode())

@@ -1,0 +1,45 @@
+// kernels.h — host-side launch interface of the sm_100a kernels (internal to libfhe_b200.so).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace fhe {
+
+struct TowerMod;
+
+// Device-resident description of one ring: (N, T, q_i, psi_i) plus the tables PreCompute builds
+// in the reference (transformnat-impl.h:708-763), already uploaded to HBM.
+struct RingDev {
+    uint32_t N, logN, T;
+    const TowerMod* mods;        // [T]
+    const ulonglong2* twF;       // [T][N]  {psi^bitrev(i), companion}
+    const ulonglong2* twI;       // [T][N]  {psi^-bitrev(i), companion}
+    const ulonglong2* invc;      // [T][2]  {N^-1, companion}, {WI[1]*N^-1, companion}
+};
+
+enum EwOp { EW_ADD = 0, EW_SUB = 1, EW_MUL = 2 };
+
+// dst = a (op) b over [batch][T][N]; dst may alias a or b.
+cudaError_t launch_elementwise(const RingDev& r, int op, uint64_t* dst, const uint64_t* a,
+                               const uint64_t* b, size_t batch, cudaStream_t st);
+// dst[i] = a[i] (op) b[i] mod q over a flat vector of n words (one modulus), any n.
+cudaError_t launch_vec(int op, uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t n,
+                       uint64_t q, cudaStream_t st);
+// dst[i] = a[i] (op) s mod q
+cudaError_t launch_vec_scalar(int op, uint64_t* dst, const uint64_t* a, uint64_t s, size_t n,
+                              uint64_t q, cudaStream_t st);
+// In-place forward / inverse negacyclic NTT of every tower of every batch item.
+// algo: 0 = auto, 1 = force the single-CTA shared-memory kernel (N <= 4096).
+cudaError_t launch_ntt(const RingDev& r, uint64_t* data, size_t batch, bool inverse,
+                       cudaStream_t st, int algo);
+// Counter-based uniform fill in [0, q_t) per tower (same definition as the test oracle's generator).
+cudaError_t launch_fill_uniform(const RingDev& r, uint64_t* dst, size_t batch, uint64_t seed,
+                                cudaStream_t st);
+// Integer-pipe probe: every thread runs `iters` dependent-chain-free 64x64->128 multiply-adds.
+cudaError_t launch_imad_probe(uint64_t* out, int blocks, int threads, int iters, cudaStream_t st);
+
+int kernel_launch_count();       // number of kernels launched by this library since load
+void kernel_launch_count_add(int n);
+
+}  // namespace fhe

@@ -1,0 +1,413 @@
+// ntt.cu — batched negacyclic NTT / INTT over RNS towers for sm_100a.
+//
+// Replaces, on the device, the reference's CPU kernels (citations relative to the reference tree):
+//   NumberTheoreticTransformNat::ForwardTransformToBitReverseInPlace   transformnat-impl.h:300-354
+//   NumberTheoreticTransformNat::InverseTransformFromBitReverseInPlace transformnat-impl.h:492-552
+// with the same index pattern (Cooley-Tukey natural->bit-reversed with twiddle table[m+i];
+// Gentleman-Sande bit-reversed->natural with N^-1 folded in), so outputs are bit-identical.
+//
+// Data layout in HBM: [batch][tower][N] u64, tower-major and coefficient-contiguous like the
+// reference's DCRTPoly.  Twiddles: per tower N records {w, floor(w*2^64/q)} (16 B, one LDG.128).
+//
+// Decomposition for N = 2^L, 9 <= L <= 16: N = N1 x 256.
+//   strided pass: N1-point sub-NTTs over elements 256 apart (stages 0..L-9), all columns and all
+//                 batch items of a tower share the same N1-1 twiddles;
+//   contig pass : 256-point sub-NTTs over contiguous blocks (stages L-8..L-1); a tile takes the
+//                 SAME block of up to 16 different batch items so twiddle loads are shared.
+// Each thread keeps 16 coefficients in registers and runs 4 butterfly stages per step (radix-16),
+// one shared-memory exchange per pass.  Harvey lazy reduction: forward values live in [0,4q),
+// inverse values in [0,2q); the last store of a transform reduces to [0,q).
+// HBM traffic: 32 B per coefficient per transform (two passes); twiddles amortised over the batch.
+// N <= 256 (and any N <= 4096 on request) uses one CTA per tower entirely in shared memory.
+#include "modarith.cuh"
+#include "kernels.h"
+
+namespace fhe {
+
+__device__ __forceinline__ ulonglong2 ldtw(const ulonglong2* __restrict__ p) { return __ldg(p); }
+
+// One butterfly stage J (of S) on E = 2^S register-resident coefficients.  The coefficients are
+// the sub-NTT whose twiddle prefix is P: stage J uses table[(P << J) + (e >> (S-J))].
+template <int S, int J, bool INV>
+__device__ __forceinline__ void reg_stage(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw, u32 P,
+                                          u64 q2, u64 nq) {
+    constexpr int half = 1 << (S - 1 - J);
+#pragma unroll
+    for (int g = 0; g < (1 << J); g++) {
+        ulonglong2 w = ldtw(tw + ((P << J) + g));
+#pragma unroll
+        for (int i = 0; i < half; i++) {
+            if (!INV) fwd_bf(x[g * 2 * half + i], x[g * 2 * half + i + half], w.x, w.y, q2, nq);
+            else      inv_bf(x[g * 2 * half + i], x[g * 2 * half + i + half], w.x, w.y, q2, nq);
+        }
+    }
+}
+
+// Stages [J0, J1) in transform order: ascending for the forward CT, descending for the inverse GS.
+template <int S, int J0, int J1, bool INV>
+__device__ __forceinline__ void reg_stages(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw, u32 P,
+                                           u64 q2, u64 nq) {
+    if constexpr (J0 < J1) {
+        if constexpr (!INV) {
+            reg_stage<S, J0, false>(x, tw, P, q2, nq);
+            reg_stages<S, J0 + 1, J1, false>(x, tw, P, q2, nq);
+        } else {
+            reg_stage<S, J1 - 1, true>(x, tw, P, q2, nq);
+            reg_stages<S, J0, J1 - 1, true>(x, tw, P, q2, nq);
+        }
+    }
+}
+
+template <int S, bool INV>
+__device__ __forceinline__ void reg_step(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw, u32 P,
+                                         u64 q2, u64 nq) {
+    reg_stages<S, 0, S, INV>(x, tw, P, q2, nq);
+}
+
+// Inverse step that contains the very last stage of the whole transform (global stage m = 1):
+// folds N^-1 into it like transformnat-impl.h:497-524 folds it into the first one, and reduces
+// both outputs to [0,q).  sc = {N^-1, companion}, w1 = {WI[1]*N^-1 mod q, companion}.
+template <int S>
+__device__ __forceinline__ void reg_step_inv_last(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw,
+                                                  ulonglong2 sc, ulonglong2 w1, u64 q, u64 q2, u64 nq) {
+    reg_stages<S, 1, S, true>(x, tw, 1u, q2, nq);
+    constexpr int half = 1 << (S - 1);
+#pragma unroll
+    for (int i = 0; i < half; i++) {
+        u64 s = x[i] + x[i + half];
+        u64 d = x[i] - x[i + half] + q2;
+        x[i]        = csub(shoup_lazy(s, sc.x, sc.y, nq), q);
+        x[i + half] = csub(shoup_lazy(d, w1.x, w1.y, nq), q);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Strided pass: R = 2^RL point sub-NTTs over elements 256 apart.  Tile = R rows x C columns.
+// Forward: stages 0..RL-1 of the transform (twiddle prefix 1).  Inverse: the same stages in
+// reverse order, run AFTER the contig pass, ending with the N^-1 stage.
+// ------------------------------------------------------------------------------------------
+template <int RL>
+struct StridedCfg {
+    static constexpr int A = RL < 4 ? RL : 4;          // stages done on the top bits of the row index
+    static constexpr int B = RL - A;                   // stages done on the low bits
+    static constexpr int R = 1 << RL;
+    static constexpr int C = (4096 / R) < 256 ? (4096 / R) : 256;
+    static constexpr int THREADS = R * C / 16;
+    static constexpr int GA = 16 >> A;                 // register groups per thread in step A
+    static constexpr int GB = 16 >> B;
+    static constexpr int SMEM = (B > 0) ? R * C * 8 : 0;
+};
+
+template <int RL, bool INV>
+__global__ void __launch_bounds__(StridedCfg<RL>::THREADS)
+ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
+                   const TowerMod* __restrict__ mods, const ulonglong2* __restrict__ invc,
+                   u32 T, u32 logN) {
+    using K = StridedCfg<RL>;
+    extern __shared__ __align__(16) u64 sm[];
+    constexpr int A = K::A, B = K::B, C = K::C;
+    const u32 tilesPerUnit = 256 / C;
+    const u32 unit  = blockIdx.x / tilesPerUnit;
+    const u32 cg    = blockIdx.x % tilesPerUnit;
+    const u32 tower = unit % T;
+    const u64 q = mods[tower].q, q2 = 2 * q, nq = 0ull - q;
+    const ulonglong2* tw = twAll + ((size_t)tower << logN);
+    u64* base = data + ((size_t)unit << logN) + cg * C;
+    const u32 tid = threadIdx.x;
+
+    if (!INV) {
+        // step A: top A bits of the row index live in registers
+#pragma unroll
+        for (int g = 0; g < K::GA; g++) {
+            u32 item = tid + g * K::THREADS;
+            u32 c = item % C, ulow = item / C;
+            u64 x[1 << A];
+#pragma unroll
+            for (int e = 0; e < (1 << A); e++) x[e] = base[((size_t)((e << B) + ulow) << 8) + c];
+            reg_step<A, false>(x, tw, 1u, q2, nq);
+            if (B == 0) {
+#pragma unroll
+                for (int e = 0; e < (1 << A); e++) base[((size_t)((e << B) + ulow) << 8) + c] = x[e];
+            } else {
+#pragma unroll
+                for (int e = 0; e < (1 << A); e++) sm[((e << B) + ulow) * C + c] = x[e];
+            }
+        }
+        if (B > 0) {
+            __syncthreads();
+#pragma unroll
+            for (int g = 0; g < K::GB; g++) {
+                u32 item = tid + g * K::THREADS;
+                u32 c = item % C, uhi = item / C;
+                u64 x[1 << B];
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) x[e] = sm[((uhi << B) + e) * C + c];
+                reg_step<B, false>(x, tw, (1u << A) + uhi, q2, nq);
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) base[((size_t)((uhi << B) + e) << 8) + c] = x[e];
+            }
+        }
+    } else {
+        const ulonglong2 sc = invc[2 * tower], w1 = invc[2 * tower + 1];
+        if (B > 0) {
+#pragma unroll
+            for (int g = 0; g < K::GB; g++) {
+                u32 item = tid + g * K::THREADS;
+                u32 c = item % C, uhi = item / C;
+                u64 x[1 << B];
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) x[e] = base[((size_t)((uhi << B) + e) << 8) + c];
+                reg_step<B, true>(x, tw, (1u << A) + uhi, q2, nq);
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) sm[((uhi << B) + e) * C + c] = x[e];
+            }
+            __syncthreads();
+        }
+#pragma unroll
+        for (int g = 0; g < K::GA; g++) {
+            u32 item = tid + g * K::THREADS;
+            u32 c = item % C, ulow = item / C;
+            u64 x[1 << A];
+            if (B > 0) {
+#pragma unroll
+                for (int e = 0; e < (1 << A); e++) x[e] = sm[((e << B) + ulow) * C + c];
+            } else {
+#pragma unroll
+                for (int e = 0; e < (1 << A); e++) x[e] = base[((size_t)((e << B) + ulow) << 8) + c];
+            }
+            reg_step_inv_last<A>(x, tw, sc, w1, q, q2, nq);
+#pragma unroll
+            for (int e = 0; e < (1 << A); e++) base[((size_t)((e << B) + ulow) << 8) + c] = x[e];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Contig pass: 256-point sub-NTTs over contiguous blocks (transform stages L-8..L-1).
+// Tile = 16 sub-NTTs: CB batch items x CH consecutive blocks (CB*CH = 16), 256 threads.
+// Shared layout [u][c] with row pitch 17 so both the u-major and the c-major accesses are
+// bank-conflict free.
+// ------------------------------------------------------------------------------------------
+constexpr int CT_PITCH = 17;
+constexpr int CT_SMEM  = 256 * CT_PITCH * 8;
+
+template <bool INV>
+__global__ void __launch_bounds__(256)
+ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
+                  const TowerMod* __restrict__ mods, u32 T, u32 logN, u32 batch, u32 logCB) {
+    extern __shared__ __align__(16) u64 sm[];
+    const u32 N1 = 1u << (logN - 8);
+    const u32 CB = 1u << logCB, CH = 16u >> logCB;
+    const u32 hgroups = N1 / CH;                      // N1 >= CH is guaranteed by the launcher
+    const u32 bgroups = (batch + CB - 1) / CB;
+    u32 bid = blockIdx.x;
+    const u32 hg = bid % hgroups; bid /= hgroups;
+    const u32 bg = bid % bgroups;
+    const u32 tower = bid / bgroups;
+    const u64 q = mods[tower].q, q2 = 2 * q, nq = 0ull - q;
+    const ulonglong2* tw = twAll + ((size_t)tower << logN);
+    const u32 tid = threadIdx.x;
+
+    auto blk_ptr = [&](u32 c, bool& ok, u32& h) -> u64* {
+        u32 b = bg * CB + (c & (CB - 1));
+        h = hg * CH + (c >> logCB);
+        ok = b < batch;
+        return data + (((size_t)b * T + tower) << logN) + ((size_t)h << 8);
+    };
+
+    if (!INV) {
+        {   // step A: lanes run along the low 4 bits of u (coalesced), registers hold the top 4
+            u32 ulow = tid & 15, c = tid >> 4, h; bool ok;
+            u64* p = blk_ptr(c, ok, h);
+            u64 x[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) x[e] = ok ? p[e * 16 + ulow] : 0ull;
+            reg_step<4, false>(x, tw, N1 + h, q2, nq);
+#pragma unroll
+            for (int e = 0; e < 16; e++) sm[(e * 16 + ulow) * CT_PITCH + c] = x[e];
+        }
+        __syncthreads();
+        {   // step B: lanes run along c, registers hold the low 4 bits of u
+            u32 c = tid & 15, uhi = tid >> 4, h; bool ok;
+            (void)blk_ptr(c, ok, h);
+            u64 x[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) x[e] = sm[(uhi * 16 + e) * CT_PITCH + c];
+            reg_step<4, false>(x, tw, ((N1 + h) << 4) + uhi, q2, nq);
+#pragma unroll
+            for (int e = 0; e < 16; e++) sm[(uhi * 16 + e) * CT_PITCH + c] = csub(csub(x[e], q2), q);
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 16; k++) {               // coalesced write-back, fully reduced
+            u32 h; bool ok;
+            u64* p = blk_ptr(k, ok, h);
+            if (ok) p[tid] = sm[tid * CT_PITCH + k];
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            u32 h; bool ok;
+            u64* p = blk_ptr(k, ok, h);
+            sm[tid * CT_PITCH + k] = ok ? p[tid] : 0ull;
+        }
+        __syncthreads();
+        {
+            u32 c = tid & 15, uhi = tid >> 4, h; bool ok;
+            (void)blk_ptr(c, ok, h);
+            u64 x[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) x[e] = sm[(uhi * 16 + e) * CT_PITCH + c];
+            reg_step<4, true>(x, tw, ((N1 + h) << 4) + uhi, q2, nq);
+#pragma unroll
+            for (int e = 0; e < 16; e++) sm[(uhi * 16 + e) * CT_PITCH + c] = x[e];
+        }
+        __syncthreads();
+        {
+            u32 ulow = tid & 15, c = tid >> 4, h; bool ok;
+            u64* p = blk_ptr(c, ok, h);
+            u64 x[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) x[e] = sm[(e * 16 + ulow) * CT_PITCH + c];
+            reg_step<4, true>(x, tw, N1 + h, q2, nq);
+            if (ok) {
+#pragma unroll
+                for (int e = 0; e < 16; e++) p[e * 16 + ulow] = x[e];   // lazily reduced, [0,2q)
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Small rings (N <= 4096): one CTA per (batch, tower) unit, whole tower in shared memory,
+// radix-2 stages with fully reduced butterflies exactly as the reference orders them.
+// ------------------------------------------------------------------------------------------
+template <bool INV>
+__global__ void __launch_bounds__(256)
+ntt_small_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
+                 const TowerMod* __restrict__ mods, const ulonglong2* __restrict__ invc,
+                 u32 T, u32 logN) {
+    extern __shared__ __align__(16) u64 sm[];
+    const u32 N = 1u << logN;
+    const u32 unit = blockIdx.x, tower = unit % T;
+    const u64 q = mods[tower].q;
+    const ulonglong2* tw = twAll + ((size_t)tower << logN);
+    u64* p = data + ((size_t)unit << logN);
+    for (u32 i = threadIdx.x; i < N; i += blockDim.x) sm[i] = p[i];
+    __syncthreads();
+    if (!INV) {
+        for (u32 s = 0; s < logN; s++) {              // m = 2^s, t = N >> (s+1)
+            u32 lt = logN - 1 - s;
+            for (u32 k = threadIdx.x; k < N / 2; k += blockDim.x) {
+                u32 i = k >> lt, j = ((i << (lt + 1)) | (k & ((1u << lt) - 1)));
+                ulonglong2 w = ldtw(tw + (1u << s) + i);
+                u64 lo = sm[j], of = shoup(sm[j + (1u << lt)], w.x, w.y, q);
+                sm[j] = addmod(lo, of, q);
+                sm[j + (1u << lt)] = submod(lo, of, q);
+            }
+            __syncthreads();
+        }
+    } else {
+        const ulonglong2 sc = invc[2 * tower];
+        for (int s = (int)logN - 1; s >= 0; s--) {
+            u32 lt = logN - 1 - s;
+            for (u32 k = threadIdx.x; k < N / 2; k += blockDim.x) {
+                u32 i = k >> lt, j = ((i << (lt + 1)) | (k & ((1u << lt) - 1)));
+                ulonglong2 w = ldtw(tw + (1u << s) + i);
+                u64 lo = sm[j], hi = sm[j + (1u << lt)];
+                sm[j] = addmod(lo, hi, q);
+                sm[j + (1u << lt)] = shoup(submod(lo, hi, q), w.x, w.y, q);
+            }
+            __syncthreads();
+        }
+        for (u32 i = threadIdx.x; i < N; i += blockDim.x) sm[i] = shoup(sm[i], sc.x, sc.y, q);
+        __syncthreads();
+    }
+    for (u32 i = threadIdx.x; i < N; i += blockDim.x) p[i] = sm[i];
+}
+
+// ------------------------------------------------------------------------------------------
+// Launchers
+// ------------------------------------------------------------------------------------------
+template <int RL, bool INV>
+static cudaError_t launch_strided_t(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
+    using K = StridedCfg<RL>;
+    static bool attr_done = false;
+    if (!attr_done && K::SMEM > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(ntt_strided_kernel<RL, INV>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    size_t grid = batch * r.T * (256 / K::C);
+    ntt_strided_kernel<RL, INV><<<(unsigned)grid, K::THREADS, K::SMEM, st>>>(
+        data, INV ? r.twI : r.twF, r.mods, r.invc, r.T, r.logN);
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
+}
+
+template <bool INV>
+static cudaError_t launch_strided(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
+    switch (r.logN - 8) {
+        case 1: return launch_strided_t<1, INV>(r, data, batch, st);
+        case 2: return launch_strided_t<2, INV>(r, data, batch, st);
+        case 3: return launch_strided_t<3, INV>(r, data, batch, st);
+        case 4: return launch_strided_t<4, INV>(r, data, batch, st);
+        case 5: return launch_strided_t<5, INV>(r, data, batch, st);
+        case 6: return launch_strided_t<6, INV>(r, data, batch, st);
+        case 7: return launch_strided_t<7, INV>(r, data, batch, st);
+        case 8: return launch_strided_t<8, INV>(r, data, batch, st);
+    }
+    return cudaErrorInvalidValue;
+}
+
+template <bool INV>
+static cudaError_t launch_contig(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
+    const u32 N1 = r.N >> 8;
+    u32 logCB = 0;                                   // batch items per tile: largest 2^k <= min(batch,16) ...
+    while (logCB < 4 && (2u << logCB) <= batch) logCB++;
+    while ((16u >> logCB) > N1) logCB++;             // ... but never more blocks per tile than the ring has
+    const u32 CB = 1u << logCB, CH = 16u >> logCB;
+    size_t grid = (size_t)r.T * ((batch + CB - 1) / CB) * (N1 / CH);
+    static bool attr_done[2] = {false, false};
+    if (!attr_done[INV]) {
+        cudaError_t e = cudaFuncSetAttribute(ntt_contig_kernel<INV>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
+        if (e != cudaSuccess) return e;
+        attr_done[INV] = true;
+    }
+    ntt_contig_kernel<INV><<<(unsigned)grid, 256, CT_SMEM, st>>>(data, INV ? r.twI : r.twF, r.mods,
+                                                                 r.T, r.logN, (u32)batch, logCB);
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
+}
+
+template <bool INV>
+static cudaError_t launch_small(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
+    size_t smem = (size_t)r.N * 8;
+    ntt_small_kernel<INV><<<(unsigned)(batch * r.T), 256, smem, st>>>(data, INV ? r.twI : r.twF,
+                                                                     r.mods, r.invc, r.T, r.logN);
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_ntt(const RingDev& r, uint64_t* data, size_t batch, bool inverse,
+                       cudaStream_t st, int algo) {
+    if (batch == 0) return cudaSuccess;
+    if (batch * r.T * 16 > 0x7fffffffull) return cudaErrorInvalidValue;   // grid.x limit
+    u64* d = reinterpret_cast<u64*>(data);
+    if (r.logN <= 8 || (algo == 1 && r.logN <= 12))
+        return inverse ? launch_small<true>(r, d, batch, st) : launch_small<false>(r, d, batch, st);
+    if (r.logN > 16) return cudaErrorInvalidValue;
+    cudaError_t e;
+    if (!inverse) {
+        e = launch_strided<false>(r, d, batch, st);
+        if (e != cudaSuccess) return e;
+        return launch_contig<false>(r, d, batch, st);
+    }
+    e = launch_contig<true>(r, d, batch, st);
+    if (e != cudaSuccess) return e;
+    return launch_strided<true>(r, d, batch, st);
+}
+
+}  // namespace fhe

@@ -1,0 +1,716 @@
+// runtime.cu — the C ABI (include/fhe_b200.h): device context, stream pool, arena allocator,
+// ring/table management and the host-operand pipelines.  Replaces the reference's UPMEM host
+// runtime (src/core/include/pim/PimManager.h, src/core/pim/host/PimManager.cpp, pim/DpuMemory.h).
+// No CPU fallback lives here: every compute entry point launches a CUDA kernel or fails.
+#include "fhe_b200.h"
+#include "pim/common.h"
+
+#include "hostmath.h"
+#include "kernels.h"
+#include "modarith.cuh"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+using namespace fhe;
+
+// ---------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CUDA_TRY(expr)                                                                        \
+    do {                                                                                      \
+        cudaError_t e__ = (expr);                                                             \
+        if (e__ != cudaSuccess)                                                               \
+            return fail(FHE_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__),   \
+                        __FILE__, __LINE__);                                                  \
+    } while (0)
+
+extern "C" const char* fhe_last_error(void) { return g_err; }
+extern "C" const char* fhe_version(void) { return "fhe_b200 0.1 (sm_100a)"; }
+extern "C" long fhe_launch_count(void) { return kernel_launch_count(); }
+
+// ---------------------------------------------------------------------------------------------
+// device arena: slabs obtained with cudaMalloc, first-fit free list with coalescing inside a slab.
+// Takes the place of DpuMemory's 64 MB / 4 KB block map (pim/DpuMemory.h:11-82), sized for HBM.
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+constexpr size_t ARENA_ALIGN = 256;
+
+struct Slab {
+    char* base = nullptr;
+    size_t size = 0;
+    std::map<size_t, size_t> free_;            // offset -> length
+};
+
+struct Arena {
+    std::mutex mu;
+    std::vector<Slab> slabs;
+    std::map<uintptr_t, std::pair<int, size_t>> live;   // ptr -> (slab, length)
+    size_t slab_bytes = 256ull << 20;
+    size_t reserved = 0, in_use = 0;
+
+    int alloc(size_t bytes, void** out) {
+        if (bytes == 0) bytes = ARENA_ALIGN;
+        bytes = (bytes + ARENA_ALIGN - 1) / ARENA_ALIGN * ARENA_ALIGN;
+        std::lock_guard<std::mutex> lk(mu);
+        for (int pass = 0; pass < 2; pass++) {
+            for (size_t s = 0; s < slabs.size(); s++) {
+                auto& fl = slabs[s].free_;
+                for (auto it = fl.begin(); it != fl.end(); ++it) {
+                    if (it->second < bytes) continue;
+                    size_t off = it->first, len = it->second;
+                    fl.erase(it);
+                    if (len > bytes) fl[off + bytes] = len - bytes;
+                    *out = slabs[s].base + off;
+                    live[(uintptr_t)*out] = {(int)s, bytes};
+                    in_use += bytes;
+                    return FHE_OK;
+                }
+            }
+            if (pass == 1) break;
+            Slab sl;
+            sl.size = std::max(slab_bytes, bytes);
+            cudaError_t e = cudaMalloc((void**)&sl.base, sl.size);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                return fail(FHE_ENOMEM, "device arena: cudaMalloc(%zu) failed: %s", sl.size,
+                            cudaGetErrorString(e));
+            }
+            sl.free_[0] = sl.size;
+            reserved += sl.size;
+            slabs.push_back(std::move(sl));
+        }
+        return fail(FHE_ENOMEM, "device arena: no block of %zu bytes", bytes);
+    }
+
+    int release(void* p) {
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = live.find((uintptr_t)p);
+        if (it == live.end()) return fail(FHE_EINVAL, "fhe_free: %p is not a live arena block", p);
+        int s = it->second.first;
+        size_t len = it->second.second, off = (char*)p - slabs[s].base;
+        live.erase(it);
+        in_use -= len;
+        auto& fl = slabs[s].free_;
+        auto nx = fl.lower_bound(off);
+        if (nx != fl.end() && off + len == nx->first) { len += nx->second; nx = fl.erase(nx); }
+        if (nx != fl.begin()) {
+            auto pv = std::prev(nx);
+            if (pv->first + pv->second == off) { off = pv->first; len += pv->second; fl.erase(pv); }
+        }
+        fl[off] = len;
+        return FHE_OK;
+    }
+
+    void destroy() {
+        for (auto& s : slabs) cudaFree(s.base);
+        slabs.clear();
+        live.clear();
+        reserved = in_use = 0;
+    }
+};
+
+struct Timer { cudaEvent_t a = nullptr, b = nullptr; };
+
+}  // namespace
+
+struct fhe_ctx {
+    int device = 0;
+    std::vector<cudaStream_t> streams;
+    Arena arena;
+    std::mutex mu;
+    std::map<int, Timer> timers;
+    std::vector<void*> pinned;
+};
+
+struct fhe_ring {
+    fhe_ctx* ctx = nullptr;
+    RingDev dev{};
+    std::vector<uint64_t> q, psi;
+    bool has_ntt = false;      // psi given and primitive for every tower
+    bool ntt_identity = false; // every psi is 0 or 1: SwitchFormat leaves data untouched (transformnat-impl.h:580-582)
+    void* d_mods = nullptr;
+    void* d_twF = nullptr;
+    void* d_twI = nullptr;
+    void* d_invc = nullptr;
+};
+
+static int get_stream(fhe_ctx* ctx, int stream, cudaStream_t* out) {
+    if (!ctx) return fail(FHE_EINVAL, "null context");
+    if (stream == FHE_STREAM_LEGACY) { *out = cudaStreamLegacy; return FHE_OK; }
+    if (stream < 0 || stream >= (int)ctx->streams.size())
+        return fail(FHE_EINVAL, "stream index %d out of range [0,%zu)", stream, ctx->streams.size());
+    *out = ctx->streams[stream];
+    return FHE_OK;
+}
+
+static long opt_value(const char* opts, const char* key, long dflt) {
+    if (!opts) return dflt;
+    std::string s(opts), k = std::string(key) + "=";
+    size_t p = 0;
+    while ((p = s.find(k, p)) != std::string::npos) {
+        if (p == 0 || s[p - 1] == ',' || s[p - 1] == ' ') return atol(s.c_str() + p + k.size());
+        p += k.size();
+    }
+    return dflt;
+}
+
+// ---------------------------------------------------------------------------------------------
+// runtime
+// ---------------------------------------------------------------------------------------------
+extern "C" int fhe_init(int device, const char* opts, fhe_ctx** out) {
+    if (!out) return fail(FHE_EINVAL, "fhe_init: out is null");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(FHE_ENODEV, "fhe_init: no CUDA device (%s); this backend has no CPU fallback",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    }
+    if (device < 0 || device >= n) return fail(FHE_EINVAL, "fhe_init: device %d not in [0,%d)", device, n);
+    CUDA_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(FHE_ENODEV, "fhe_init: device %d is sm_%d%d; this library holds sm_100a code only",
+                    device, prop.major, prop.minor);
+    auto* ctx = new fhe_ctx;
+    ctx->device = device;
+    long ns = std::max(1l, std::min(64l, opt_value(opts, "streams", 4)));
+    ctx->arena.slab_bytes = (size_t)std::max(1l, opt_value(opts, "arena_mb", 256)) << 20;
+    for (long i = 0; i < ns; i++) {
+        cudaStream_t s;
+        e = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
+        if (e != cudaSuccess) {
+            delete ctx;
+            return fail(FHE_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(e));
+        }
+        ctx->streams.push_back(s);
+    }
+    *out = ctx;
+    return FHE_OK;
+}
+
+extern "C" int fhe_shutdown(fhe_ctx* ctx) {
+    if (!ctx) return FHE_OK;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    for (auto& t : ctx->timers) { cudaEventDestroy(t.second.a); cudaEventDestroy(t.second.b); }
+    for (auto s : ctx->streams) cudaStreamDestroy(s);
+    for (void* p : ctx->pinned) cudaFreeHost(p);
+    ctx->arena.destroy();
+    delete ctx;
+    return FHE_OK;
+}
+
+extern "C" int fhe_device(const fhe_ctx* ctx) { return ctx ? ctx->device : -1; }
+extern "C" int fhe_num_streams(const fhe_ctx* ctx) { return ctx ? (int)ctx->streams.size() : 0; }
+
+extern "C" int fhe_sync(fhe_ctx* ctx, int stream) {
+    if (!ctx) return fail(FHE_EINVAL, "null context");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    if (stream == -2) { CUDA_TRY(cudaDeviceSynchronize()); return FHE_OK; }
+    cudaStream_t s;
+    int rc = get_stream(ctx, stream, &s);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(s));
+    return FHE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// memory
+// ---------------------------------------------------------------------------------------------
+extern "C" int fhe_alloc(fhe_ctx* ctx, size_t bytes, fhe_dptr* out) {
+    if (!ctx || !out) return fail(FHE_EINVAL, "fhe_alloc: null argument");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    void* p = nullptr;
+    int rc = ctx->arena.alloc(bytes, &p);
+    if (rc) return rc;
+    *out = (fhe_dptr)(uintptr_t)p;
+    return FHE_OK;
+}
+
+extern "C" int fhe_free(fhe_ctx* ctx, fhe_dptr p) {
+    if (!ctx) return fail(FHE_EINVAL, "null context");
+    if (!p) return FHE_OK;
+    return ctx->arena.release((void*)(uintptr_t)p);
+}
+
+extern "C" int fhe_arena_stats(fhe_ctx* ctx, size_t* reserved_bytes, size_t* in_use_bytes) {
+    if (!ctx) return fail(FHE_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(ctx->arena.mu);
+    if (reserved_bytes) *reserved_bytes = ctx->arena.reserved;
+    if (in_use_bytes) *in_use_bytes = ctx->arena.in_use;
+    return FHE_OK;
+}
+
+extern "C" int fhe_host_alloc(fhe_ctx* ctx, size_t bytes, void** out) {
+    if (!ctx || !out) return fail(FHE_EINVAL, "fhe_host_alloc: null argument");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(cudaMallocHost(out, bytes ? bytes : 1));
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->pinned.push_back(*out);
+    return FHE_OK;
+}
+
+extern "C" int fhe_host_free(fhe_ctx* ctx, void* p) {
+    if (!ctx) return fail(FHE_EINVAL, "null context");
+    if (!p) return FHE_OK;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        auto it = std::find(ctx->pinned.begin(), ctx->pinned.end(), p);
+        if (it == ctx->pinned.end()) return fail(FHE_EINVAL, "fhe_host_free: unknown pointer");
+        ctx->pinned.erase(it);
+    }
+    CUDA_TRY(cudaFreeHost(p));
+    return FHE_OK;
+}
+
+static int copy_async(fhe_ctx* ctx, void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, int stream) {
+    cudaStream_t s;
+    int rc = get_stream(ctx, stream, &s);
+    if (rc) return rc;
+    if (bytes == 0) return FHE_OK;
+    if (!dst || !src) return fail(FHE_EINVAL, "copy: null pointer");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, kind, s));
+    return FHE_OK;
+}
+extern "C" int fhe_h2d(fhe_ctx* ctx, fhe_dptr dst, const void* src, size_t bytes, int stream) {
+    return copy_async(ctx, (void*)(uintptr_t)dst, src, bytes, cudaMemcpyHostToDevice, stream);
+}
+extern "C" int fhe_d2h(fhe_ctx* ctx, void* dst, fhe_dptr src, size_t bytes, int stream) {
+    return copy_async(ctx, dst, (const void*)(uintptr_t)src, bytes, cudaMemcpyDeviceToHost, stream);
+}
+extern "C" int fhe_d2d(fhe_ctx* ctx, fhe_dptr dst, fhe_dptr src, size_t bytes, int stream) {
+    return copy_async(ctx, (void*)(uintptr_t)dst, (const void*)(uintptr_t)src, bytes, cudaMemcpyDeviceToDevice, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// timing
+// ---------------------------------------------------------------------------------------------
+extern "C" int fhe_timer_start(fhe_ctx* ctx, int stream) {
+    cudaStream_t s;
+    int rc = get_stream(ctx, stream, &s);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    Timer* t;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        t = &ctx->timers[stream];
+    }
+    if (!t->a) { CUDA_TRY(cudaEventCreate(&t->a)); CUDA_TRY(cudaEventCreate(&t->b)); }
+    CUDA_TRY(cudaEventRecord(t->a, s));
+    return FHE_OK;
+}
+
+extern "C" int fhe_timer_stop(fhe_ctx* ctx, int stream, float* elapsed_ms) {
+    cudaStream_t s;
+    int rc = get_stream(ctx, stream, &s);
+    if (rc) return rc;
+    Timer* t;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        auto it = ctx->timers.find(stream);
+        if (it == ctx->timers.end() || !it->second.a) return fail(FHE_EINVAL, "fhe_timer_stop without fhe_timer_start");
+        t = &it->second;
+    }
+    CUDA_TRY(cudaEventRecord(t->b, s));
+    CUDA_TRY(cudaEventSynchronize(t->b));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, t->a, t->b));
+    if (elapsed_ms) *elapsed_ms = ms;
+    return FHE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// parameters
+// ---------------------------------------------------------------------------------------------
+extern "C" int fhe_gen_params(uint32_t nbits, uint32_t N, uint32_t towers, uint64_t* q, uint64_t* psi) {
+    if (!q || !psi) return fail(FHE_EINVAL, "fhe_gen_params: null output");
+    if (nbits < 4 || nbits > 60) return fail(FHE_EINVAL, "fhe_gen_params: nbits %u not in [4,60]", nbits);
+    if (N == 0 || (N & (N - 1))) return fail(FHE_EINVAL, "fhe_gen_params: N must be a power of two");
+    uint64_t m = 2ull * N, prev = host::first_prime(nbits, m);
+    for (uint32_t i = 0; i < towers; i++) {
+        prev = host::previous_prime(prev, m);
+        if (prev <= m) return fail(FHE_EINVAL, "fhe_gen_params: ran out of %u-bit primes = 1 mod %llu", nbits, (unsigned long long)m);
+        q[i] = prev;
+        psi[i] = host::root_of_unity(m, prev);
+    }
+    return FHE_OK;
+}
+
+extern "C" uint64_t fhe_root_of_unity(uint64_t m, uint64_t q) { return host::root_of_unity(m, q); }
+
+// ---------------------------------------------------------------------------------------------
+// ring
+// ---------------------------------------------------------------------------------------------
+static TowerMod make_mod(uint64_t q) {
+    TowerMod m;
+    unsigned b = host::msb(q);
+    m.q = q;
+    m.mu = (uint64_t)(((host::u128)1 << (2 * b + 3)) / q);
+    m.n = b - 2;
+    m.s = b + 5;
+    m.pad = 0;
+    return m;
+}
+
+extern "C" int fhe_ring_destroy(fhe_ring* r) {
+    if (!r) return FHE_OK;
+    fhe_ctx* c = r->ctx;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    if (r->d_mods) c->arena.release(r->d_mods);
+    if (r->d_twF) c->arena.release(r->d_twF);
+    if (r->d_twI) c->arena.release(r->d_twI);
+    if (r->d_invc) c->arena.release(r->d_invc);
+    delete r;
+    return FHE_OK;
+}
+
+extern "C" int fhe_ring_create(fhe_ctx* ctx, uint32_t N, uint32_t T, const uint64_t* q, const uint64_t* psi,
+                               fhe_ring** out) {
+    if (!ctx || !q || !out) return fail(FHE_EINVAL, "fhe_ring_create: null argument");
+    *out = nullptr;
+    if (N == 0 || (N & (N - 1)) || N > 65536) return fail(FHE_EINVAL, "fhe_ring_create: N=%u must be a power of two <= 65536", N);
+    if (T == 0 || T > 4096) return fail(FHE_EINVAL, "fhe_ring_create: towers=%u not in [1,4096]", T);
+    for (uint32_t t = 0; t < T; t++)
+        if (q[t] < 4 || q[t] >= (1ull << 61))
+            return fail(FHE_EINVAL, "fhe_ring_create: modulus %u = %llu not in [4, 2^61)", t, (unsigned long long)q[t]);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    auto* r = new fhe_ring;
+    r->ctx = ctx;
+    r->q.assign(q, q + T);
+    r->dev.N = N; r->dev.T = T; r->dev.logN = host::msb(N) - 1;
+
+    std::vector<TowerMod> mods(T);
+    for (uint32_t t = 0; t < T; t++) mods[t] = make_mod(q[t]);
+    int rc = ctx->arena.alloc(sizeof(TowerMod) * T, &r->d_mods);
+    if (rc) { fhe_ring_destroy(r); return rc; }
+    cudaError_t e = cudaMemcpy(r->d_mods, mods.data(), sizeof(TowerMod) * T, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { fhe_ring_destroy(r); return fail(FHE_ECUDA, "upload moduli: %s", cudaGetErrorString(e)); }
+    r->dev.mods = (const TowerMod*)r->d_mods;
+
+    if (psi) {
+        r->psi.assign(psi, psi + T);
+        uint32_t trivial = 0;
+        for (uint32_t t = 0; t < T; t++) trivial += (psi[t] == 0 || psi[t] == 1);
+        if (trivial == T) {
+            r->ntt_identity = true;
+        } else if (trivial != 0) {
+            fhe_ring_destroy(r);
+            return fail(FHE_EUNSUPPORTED, "fhe_ring_create: mixing trivial (0/1) and real roots of unity is not supported");
+        } else {
+            for (uint32_t t = 0; t < T; t++) {
+                bool ok = N == 1 ? (psi[t] % q[t] == q[t] - 1) : (host::powmod(psi[t], N, q[t]) == q[t] - 1);
+                if (!ok || psi[t] >= q[t]) {
+                    fhe_ring_destroy(r);
+                    return fail(FHE_EINVAL, "fhe_ring_create: psi[%u]=%llu is not a primitive %u-th root of unity mod %llu",
+                                t, (unsigned long long)psi[t], 2 * N, (unsigned long long)q[t]);
+                }
+            }
+            size_t tabBytes = (size_t)T * N * 16;
+            std::vector<uint64_t> hF((size_t)T * N * 2), hI((size_t)T * N * 2), hC((size_t)T * 4);
+            unsigned nth = std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), T);
+            std::vector<std::thread> pool;
+            for (unsigned w = 0; w < nth; w++)
+                pool.emplace_back([&, w]() {
+                    host::TowerTables tt;
+                    for (uint32_t t = w; t < T; t += nth) {
+                        host::precompute(psi[t], N, q[t], tt);
+                        memcpy(&hF[(size_t)t * N * 2], tt.twF.data(), (size_t)N * 16);
+                        memcpy(&hI[(size_t)t * N * 2], tt.twI.data(), (size_t)N * 16);
+                        memcpy(&hC[(size_t)t * 4], tt.invc, 32);
+                    }
+                });
+            for (auto& th : pool) th.join();
+            if ((rc = ctx->arena.alloc(tabBytes, &r->d_twF)) || (rc = ctx->arena.alloc(tabBytes, &r->d_twI)) ||
+                (rc = ctx->arena.alloc((size_t)T * 32, &r->d_invc))) {
+                fhe_ring_destroy(r);
+                return rc;
+            }
+            if ((e = cudaMemcpy(r->d_twF, hF.data(), tabBytes, cudaMemcpyHostToDevice)) != cudaSuccess ||
+                (e = cudaMemcpy(r->d_twI, hI.data(), tabBytes, cudaMemcpyHostToDevice)) != cudaSuccess ||
+                (e = cudaMemcpy(r->d_invc, hC.data(), (size_t)T * 32, cudaMemcpyHostToDevice)) != cudaSuccess) {
+                fhe_ring_destroy(r);
+                return fail(FHE_ECUDA, "upload twiddle tables: %s", cudaGetErrorString(e));
+            }
+            r->dev.twF = (const ulonglong2*)r->d_twF;
+            r->dev.twI = (const ulonglong2*)r->d_twI;
+            r->dev.invc = (const ulonglong2*)r->d_invc;
+            r->has_ntt = true;
+        }
+    }
+    *out = r;
+    return FHE_OK;
+}
+
+extern "C" uint32_t fhe_ring_n(const fhe_ring* r) { return r ? r->dev.N : 0; }
+extern "C" uint32_t fhe_ring_towers(const fhe_ring* r) { return r ? r->dev.T : 0; }
+
+extern "C" int fhe_ring_table(const fhe_ring* r, uint32_t tower, int which, uint64_t* out) {
+    if (!r || !out) return fail(FHE_EINVAL, "fhe_ring_table: null argument");
+    if (!r->has_ntt) return fail(FHE_EINVAL, "fhe_ring_table: ring has no NTT tables");
+    if (tower >= r->dev.T || which < 0 || which > 3) return fail(FHE_EINVAL, "fhe_ring_table: bad tower/table");
+    size_t N = r->dev.N;
+    std::vector<uint64_t> tmp(2 * N);
+    const void* src = (const char*)(which < 2 ? r->d_twF : r->d_twI) + (size_t)tower * N * 16;
+    CUDA_TRY(cudaSetDevice(r->ctx->device));
+    CUDA_TRY(cudaMemcpy(tmp.data(), src, N * 16, cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < N; i++) out[i] = tmp[2 * i + (which & 1)];
+    return FHE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// hot path, device-resident operands
+// ---------------------------------------------------------------------------------------------
+static int ring_stream(fhe_ring* r, int stream, cudaStream_t* s) {
+    if (!r) return fail(FHE_EINVAL, "null ring");
+    int rc = get_stream(r->ctx, stream, s);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(r->ctx->device));
+    return FHE_OK;
+}
+
+extern "C" int fhe_dcrt_op(fhe_ring* r, int op, fhe_dptr dst, fhe_dptr a, fhe_dptr b, size_t batch, int stream) {
+    cudaStream_t s;
+    int rc = ring_stream(r, stream, &s);
+    if (rc) return rc;
+    if (op < FHE_OP_ADD || op > FHE_OP_MUL) return fail(FHE_EINVAL, "fhe_dcrt_op: unknown op %d", op);
+    if (batch == 0) return FHE_OK;
+    if (!dst || !a || !b) return fail(FHE_EINVAL, "fhe_dcrt_op: null device pointer");
+    if (r->dev.N == 1 && ((batch * r->dev.T) & 1)) return fail(FHE_EUNSUPPORTED, "fhe_dcrt_op: N=1 needs an even number of towers*batch");
+    CUDA_TRY(launch_elementwise(r->dev, op, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)a,
+                                (const uint64_t*)(uintptr_t)b, batch, s));
+    return FHE_OK;
+}
+
+extern "C" int fhe_ntt_algo(fhe_ring* r, fhe_dptr x, size_t batch, int inverse, int algo, int stream) {
+    cudaStream_t s;
+    int rc = ring_stream(r, stream, &s);
+    if (rc) return rc;
+    if (r->ntt_identity) return FHE_OK;       // psi in {0,1}: the reference returns untouched
+    if (!r->has_ntt) return fail(FHE_EINVAL, "fhe_ntt: ring was created without roots of unity");
+    if (batch == 0) return FHE_OK;
+    if (!x) return fail(FHE_EINVAL, "fhe_ntt: null device pointer");
+    if (r->dev.N == 1) return FHE_OK;
+    CUDA_TRY(launch_ntt(r->dev, (uint64_t*)(uintptr_t)x, batch, inverse != 0, s, algo));
+    return FHE_OK;
+}
+extern "C" int fhe_ntt_forward(fhe_ring* r, fhe_dptr x, size_t batch, int stream) { return fhe_ntt_algo(r, x, batch, 0, 0, stream); }
+extern "C" int fhe_ntt_inverse(fhe_ring* r, fhe_dptr x, size_t batch, int stream) { return fhe_ntt_algo(r, x, batch, 1, 0, stream); }
+
+extern "C" int fhe_poly_mul(fhe_ring* r, fhe_dptr c, fhe_dptr a, fhe_dptr b, size_t batch, int stream) {
+    if (c == a || c == b) return fail(FHE_EINVAL, "fhe_poly_mul: c must not alias an input");
+    int rc;
+    if ((rc = fhe_ntt_forward(r, a, batch, stream))) return rc;
+    if (a != b && (rc = fhe_ntt_forward(r, b, batch, stream))) return rc;
+    if ((rc = fhe_dcrt_op(r, FHE_OP_MUL, c, a, b, batch, stream))) return rc;
+    return fhe_ntt_inverse(r, c, batch, stream);
+}
+
+extern "C" int fhe_fill_uniform(fhe_ring* r, fhe_dptr dst, size_t batch, uint64_t seed, int stream) {
+    cudaStream_t s;
+    int rc = ring_stream(r, stream, &s);
+    if (rc) return rc;
+    if (batch && !dst) return fail(FHE_EINVAL, "fhe_fill_uniform: null device pointer");
+    CUDA_TRY(launch_fill_uniform(r->dev, (uint64_t*)(uintptr_t)dst, batch, seed, s));
+    return FHE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// flat vectors with explicit modulus
+// ---------------------------------------------------------------------------------------------
+static int check_vec_mod(int op, uint64_t q) {
+    if (op < FHE_OP_ADD || op > FHE_OP_MUL) return fail(FHE_EINVAL, "unknown op %d", op);
+    if (q == 0) return fail(FHE_EINVAL, "modulus is zero");
+    if (op == FHE_OP_MUL && (q < 4 || q >= (1ull << 61)))
+        return fail(FHE_EUNSUPPORTED, "modular multiply needs 4 <= modulus < 2^61 (got %llu)", (unsigned long long)q);
+    return FHE_OK;
+}
+
+extern "C" int fhe_vec_op(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, fhe_dptr b, size_t n, uint64_t q, int stream) {
+    cudaStream_t s;
+    int rc = get_stream(ctx, stream, &s);
+    if (rc || (rc = check_vec_mod(op, q))) return rc;
+    if (n == 0) return FHE_OK;
+    if (!dst || !a || !b) return fail(FHE_EINVAL, "fhe_vec_op: null device pointer");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(launch_vec(op, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)a, (const uint64_t*)(uintptr_t)b, n, q, s));
+    return FHE_OK;
+}
+
+extern "C" int fhe_vec_op_scalar(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, uint64_t scalar, size_t n,
+                                 uint64_t q, int stream) {
+    cudaStream_t s;
+    int rc = get_stream(ctx, stream, &s);
+    if (rc || (rc = check_vec_mod(op, q))) return rc;
+    if (n == 0) return FHE_OK;
+    if (!dst || !a) return fail(FHE_EINVAL, "fhe_vec_op_scalar: null device pointer");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(launch_vec_scalar(op, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)a, scalar, n, q, s));
+    return FHE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// legacy descriptor path (PimData::common_do_ops, pim/PimData.h:275-305)
+// ---------------------------------------------------------------------------------------------
+extern "C" int fhe_launch(fhe_ctx* ctx, int kernel_id, const void* desc, fhe_dptr heap_base) {
+    if (!ctx || !desc) return fail(FHE_EINVAL, "fhe_launch: null argument");
+    if (kernel_id == FHE_KERNEL_BOOT) return FHE_OK;          // boot only reset the DPU heap
+    int op;
+    switch (kernel_id) {
+        case FHE_KERNEL_MOD_ADD: op = FHE_OP_ADD; break;
+        case FHE_KERNEL_MOD_SUB: op = FHE_OP_SUB; break;
+        case FHE_KERNEL_MOD_MULT: op = FHE_OP_MUL; break;
+        case FHE_KERNEL_MOD_OPS:
+            return fail(FHE_EUNSUPPORTED, "fhe_launch: mod-ops kernels are not connected (as in the reference, pim/PimData.h:171)");
+        default: return fail(FHE_EINVAL, "fhe_launch: unknown kernel id %d", kernel_id);
+    }
+    const mod_add_sub_mult* m = (const mod_add_sub_mult*)desc;
+    size_t n = m->op1.size / sizeof(uint64_t);
+    fhe_dptr a = heap_base + m->op1.start, dst;
+    int rc;
+    switch (m->kernel) {
+        case VECTOR:    dst = heap_base + m->res.start; rc = fhe_vec_op(ctx, op, dst, a, heap_base + m->op2.start, n, m->mod, FHE_STREAM_LEGACY); break;
+        case VECTOR_EQ: rc = fhe_vec_op(ctx, op, a, a, heap_base + m->op2.start, n, m->mod, FHE_STREAM_LEGACY); break;
+        case SCALAR:    dst = heap_base + m->res.start; rc = fhe_vec_op_scalar(ctx, op, dst, a, m->op2.start, n, m->mod, FHE_STREAM_LEGACY); break;
+        case SCALAR_EQ: rc = fhe_vec_op_scalar(ctx, op, a, a, m->op2.start, n, m->mod, FHE_STREAM_LEGACY); break;
+        default: return fail(FHE_EINVAL, "fhe_launch: unknown add_sub_mul_kernel %d", (int)m->kernel);
+    }
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(cudaStreamLegacy));        // start_kernel() is DPU_SYNCHRONOUS
+    return FHE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host-operand pipelines: chunk the batch, rotate over the stream pool so that the H2D copy of
+// chunk k+1, the kernel of chunk k and the D2H copy of chunk k-1 overlap.
+// ---------------------------------------------------------------------------------------------
+namespace {
+struct HostPipe {
+    fhe_ring* r;
+    size_t item_words, chunk_items, nslots;
+    std::vector<void*> bufA, bufB;
+    HostPipe(fhe_ring* ring, bool two_operands) : r(ring) {
+        item_words = (size_t)r->dev.T * r->dev.N;
+        size_t item_bytes = item_words * 8;
+        chunk_items = std::max<size_t>(1, (32ull << 20) / item_bytes);
+        nslots = std::min<size_t>(r->ctx->streams.size(), 4);
+        (void)two_operands;
+    }
+    int reserve(size_t batch, bool two_operands) {
+        chunk_items = std::min(chunk_items, std::max<size_t>(1, batch));
+        size_t nchunks = (batch + chunk_items - 1) / chunk_items;
+        nslots = std::max<size_t>(1, std::min(nslots, nchunks));
+        for (size_t i = 0; i < nslots; i++) {
+            void* p = nullptr;
+            int rc = r->ctx->arena.alloc(chunk_items * item_words * 8, &p);
+            if (rc) return rc;
+            bufA.push_back(p);
+            if (two_operands) {
+                rc = r->ctx->arena.alloc(chunk_items * item_words * 8, &p);
+                if (rc) return rc;
+                bufB.push_back(p);
+            }
+        }
+        return FHE_OK;
+    }
+    ~HostPipe() {
+        for (void* p : bufA) r->ctx->arena.release(p);
+        for (void* p : bufB) r->ctx->arena.release(p);
+    }
+};
+}  // namespace
+
+extern "C" int fhe_dcrt_op_host(fhe_ring* r, int op, uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t batch) {
+    if (!r) return fail(FHE_EINVAL, "null ring");
+    if (op < FHE_OP_ADD || op > FHE_OP_MUL) return fail(FHE_EINVAL, "fhe_dcrt_op_host: unknown op %d", op);
+    if (batch == 0) return FHE_OK;
+    if (!dst || !a || !b) return fail(FHE_EINVAL, "fhe_dcrt_op_host: null host pointer");
+    CUDA_TRY(cudaSetDevice(r->ctx->device));
+    HostPipe hp(r, true);
+    int rc = hp.reserve(batch, true);
+    if (rc) return rc;
+    size_t k = 0;
+    for (size_t b0 = 0; b0 < batch; b0 += hp.chunk_items, k++) {
+        size_t items = std::min(hp.chunk_items, batch - b0), words = items * hp.item_words;
+        size_t slot = k % hp.nslots;
+        cudaStream_t s = r->ctx->streams[slot];
+        uint64_t* da = (uint64_t*)hp.bufA[slot];
+        uint64_t* db = (uint64_t*)hp.bufB[slot];
+        CUDA_TRY(cudaMemcpyAsync(da, a + b0 * hp.item_words, words * 8, cudaMemcpyHostToDevice, s));
+        CUDA_TRY(cudaMemcpyAsync(db, b + b0 * hp.item_words, words * 8, cudaMemcpyHostToDevice, s));
+        CUDA_TRY(launch_elementwise(r->dev, op, da, da, db, items, s));
+        CUDA_TRY(cudaMemcpyAsync(dst + b0 * hp.item_words, da, words * 8, cudaMemcpyDeviceToHost, s));
+    }
+    for (size_t i = 0; i < hp.nslots; i++) CUDA_TRY(cudaStreamSynchronize(r->ctx->streams[i]));
+    return FHE_OK;
+}
+
+extern "C" int fhe_ntt_host(fhe_ring* r, uint64_t* x, size_t batch, int inverse) {
+    if (!r) return fail(FHE_EINVAL, "null ring");
+    if (r->ntt_identity || batch == 0 || r->dev.N == 1) return FHE_OK;
+    if (!r->has_ntt) return fail(FHE_EINVAL, "fhe_ntt_host: ring was created without roots of unity");
+    if (!x) return fail(FHE_EINVAL, "fhe_ntt_host: null host pointer");
+    CUDA_TRY(cudaSetDevice(r->ctx->device));
+    HostPipe hp(r, false);
+    int rc = hp.reserve(batch, false);
+    if (rc) return rc;
+    size_t k = 0;
+    for (size_t b0 = 0; b0 < batch; b0 += hp.chunk_items, k++) {
+        size_t items = std::min(hp.chunk_items, batch - b0), words = items * hp.item_words;
+        size_t slot = k % hp.nslots;
+        cudaStream_t s = r->ctx->streams[slot];
+        uint64_t* d = (uint64_t*)hp.bufA[slot];
+        CUDA_TRY(cudaMemcpyAsync(d, x + b0 * hp.item_words, words * 8, cudaMemcpyHostToDevice, s));
+        CUDA_TRY(launch_ntt(r->dev, d, items, inverse != 0, s, 0));
+        CUDA_TRY(cudaMemcpyAsync(x + b0 * hp.item_words, d, words * 8, cudaMemcpyDeviceToHost, s));
+    }
+    for (size_t i = 0; i < hp.nslots; i++) CUDA_TRY(cudaStreamSynchronize(r->ctx->streams[i]));
+    return FHE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// diagnostics
+// ---------------------------------------------------------------------------------------------
+extern "C" int fhe_imad_probe(fhe_ctx* ctx, int blocks, int threads, int iters, float* elapsed_ms) {
+    if (!ctx) return fail(FHE_EINVAL, "null context");
+    if (blocks < 1 || threads < 1 || threads > 1024 || iters < 1) return fail(FHE_EINVAL, "fhe_imad_probe: bad launch shape");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    void* out = nullptr;
+    int rc = ctx->arena.alloc(256, &out);
+    if (rc) return rc;
+    cudaStream_t s = ctx->streams[0];
+    cudaError_t e = launch_imad_probe((uint64_t*)out, blocks, threads, 16, s);   // warm-up
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) { ctx->arena.release(out); return fail(FHE_ECUDA, "imad probe: %s", cudaGetErrorString(e)); }
+    rc = fhe_timer_start(ctx, 0);
+    if (!rc) {
+        e = launch_imad_probe((uint64_t*)out, blocks, threads, iters, s);
+        if (e != cudaSuccess) rc = fail(FHE_ECUDA, "imad probe: %s", cudaGetErrorString(e));
+    }
+    if (!rc) rc = fhe_timer_stop(ctx, 0, elapsed_ms);
+    ctx->arena.release(out);
+    return rc;
+}

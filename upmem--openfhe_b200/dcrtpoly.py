@@ -1,0 +1,246 @@
+"""Host-side handles over the C ABI, shaped like the reference's objects on this path.
+
+`DCRTPolyBatch` is a device-resident batch of DCRTPoly (layout [batch][tower][N] uint64) with the
+operator surface and error behaviour of the reference's DCRTPolyImpl for add / sub / mul /
+SwitchFormat (lattice/hal/default/dcrtpoly.h:142-200, dcrtpoly-impl.h:398-416, 2518-2524):
+`Times` throws unless both operands are in EVALUATION format, `Plus`/`Minus` throw on format or
+tower-count mismatch.  Every operation is one CUDA launch over all towers and batch items.
+numpy is used only to carry host data to and from the C ABI.
+"""
+import ctypes
+import numpy as np
+
+from . import _native as N
+
+EVALUATION = 0      # lbcrypto::Format (utils/inttypes.h)
+COEFFICIENT = 1
+
+
+def _ptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def gen_params(nbits, n, towers):
+    """q_i, psi_i as benchmark/src/poly-benchmark-16k.cpp:82-101 generates them."""
+    q = np.zeros(towers, np.uint64)
+    psi = np.zeros(towers, np.uint64)
+    N.check(N.lib.fhe_gen_params(nbits, n, towers, _ptr(q), _ptr(psi)))
+    return q, psi
+
+
+class Backend:
+    """One B200: stream pool + device arena (what PimManager::getPim hands out in the reference)."""
+
+    def __init__(self, device=0, opts=""):
+        h = ctypes.c_void_p()
+        N.check(N.lib.fhe_init(device, opts.encode() if opts else None, ctypes.byref(h)))
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_shutdown(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def num_streams(self):
+        return N.lib.fhe_num_streams(self.h)
+
+    def alloc(self, nbytes):
+        p = ctypes.c_uint64()
+        N.check(N.lib.fhe_alloc(self.h, nbytes, ctypes.byref(p)))
+        return p.value
+
+    def free(self, p):
+        N.check(N.lib.fhe_free(self.h, p))
+
+    def host_alloc(self, nwords):
+        """Pinned host buffer viewed as a numpy uint64 array."""
+        p = ctypes.c_void_p()
+        N.check(N.lib.fhe_host_alloc(self.h, nwords * 8, ctypes.byref(p)))
+        buf = (ctypes.c_uint64 * nwords).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=np.uint64)
+        arr.flags.writeable = True
+        return arr, p.value
+
+    def host_free(self, p):
+        N.check(N.lib.fhe_host_free(self.h, ctypes.c_void_p(p)))
+
+    def h2d(self, dptr, arr, stream=0):
+        arr = np.ascontiguousarray(arr, dtype=np.uint64)
+        N.check(N.lib.fhe_h2d(self.h, dptr, _ptr(arr), arr.nbytes, stream))
+        self.sync(stream)               # the host array only has to outlive this call
+        return arr
+
+    def d2h(self, dptr, nwords, stream=0, out=None):
+        if out is None:
+            out = np.empty(nwords, np.uint64)
+        N.check(N.lib.fhe_d2h(self.h, _ptr(out), dptr, nwords * 8, stream))
+        self.sync(stream)
+        return out
+
+    def sync(self, stream=-2):
+        N.check(N.lib.fhe_sync(self.h, stream))
+
+    def timer_start(self, stream=0):
+        N.check(N.lib.fhe_timer_start(self.h, stream))
+
+    def timer_stop(self, stream=0):
+        ms = ctypes.c_float()
+        N.check(N.lib.fhe_timer_stop(self.h, stream, ctypes.byref(ms)))
+        return ms.value
+
+    def vec_op(self, op, dst, a, b, n, q, stream=0):
+        N.check(N.lib.fhe_vec_op(self.h, op, dst, a, b, n, int(q), stream))
+
+    def vec_op_scalar(self, op, dst, a, s, n, q, stream=0):
+        N.check(N.lib.fhe_vec_op_scalar(self.h, op, dst, a, int(s), n, int(q), stream))
+
+    def imad_probe(self, blocks, threads, iters):
+        ms = ctypes.c_float()
+        N.check(N.lib.fhe_imad_probe(self.h, blocks, threads, iters, ctypes.byref(ms)))
+        return ms.value
+
+
+class Ring:
+    """ILDCRTParams on the device: N, moduli, roots, Barrett constants and twiddle tables in HBM."""
+
+    def __init__(self, backend, n, q, psi=None):
+        self.be = backend
+        self.n = int(n)
+        self.q = np.ascontiguousarray(q, dtype=np.uint64)
+        self.psi = None if psi is None else np.ascontiguousarray(psi, dtype=np.uint64)
+        self.towers = len(self.q)
+        h = ctypes.c_void_p()
+        N.check(N.lib.fhe_ring_create(backend.h, self.n, self.towers, _ptr(self.q),
+                                      None if self.psi is None else _ptr(self.psi), ctypes.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_ring_destroy(self.h)
+            self.h = None
+
+    def words(self, batch):
+        return batch * self.towers * self.n
+
+    def table(self, tower, which):
+        out = np.empty(self.n, np.uint64)
+        N.check(N.lib.fhe_ring_table(self.h, tower, which, _ptr(out)))
+        return out
+
+    # raw device-pointer forms (what bench.py times)
+    def op(self, op, dst, a, b, batch, stream=0):
+        N.check(N.lib.fhe_dcrt_op(self.h, op, dst, a, b, batch, stream))
+
+    def ntt(self, x, batch, inverse=False, stream=0, algo=0):
+        N.check(N.lib.fhe_ntt_algo(self.h, x, batch, 1 if inverse else 0, algo, stream))
+
+    def poly_mul(self, c, a, b, batch, stream=0):
+        N.check(N.lib.fhe_poly_mul(self.h, c, a, b, batch, stream))
+
+    def fill_uniform(self, dst, batch, seed, stream=0):
+        N.check(N.lib.fhe_fill_uniform(self.h, dst, batch, seed, stream))
+
+    # host-operand forms (end-to-end path)
+    def op_host(self, op, dst, a, b, batch):
+        N.check(N.lib.fhe_dcrt_op_host(self.h, op, _ptr(dst), _ptr(a), _ptr(b), batch))
+
+    def ntt_host(self, x, batch, inverse=False):
+        N.check(N.lib.fhe_ntt_host(self.h, _ptr(x), batch, 1 if inverse else 0))
+
+
+class DCRTPolyBatch:
+    """`batch` DCRTPolys resident in HBM; operators mirror DCRTPolyImpl."""
+
+    def __init__(self, ring, batch, fmt=EVALUATION, data=None, stream=0):
+        self.ring, self.batch, self.format, self.stream = ring, int(batch), fmt, stream
+        self.nwords = ring.words(self.batch)
+        self.dptr = ring.be.alloc(max(self.nwords, 1) * 8)
+        if data is not None:
+            data = np.ascontiguousarray(data, dtype=np.uint64).reshape(-1)
+            if data.size != self.nwords:
+                raise ValueError("data must hold batch*towers*N words")
+            ring.be.h2d(self.dptr, data, stream)
+
+    def __del__(self):
+        try:
+            if self.dptr and self.ring.be.h:
+                self.ring.be.free(self.dptr)
+        except Exception:
+            pass
+        self.dptr = 0
+
+    def to_host(self):
+        out = self.ring.be.d2h(self.dptr, self.nwords, self.stream)
+        return out.reshape(self.batch, self.ring.towers, self.ring.n)
+
+    def clone(self):
+        c = DCRTPolyBatch(self.ring, self.batch, self.format, stream=self.stream)
+        N.check(N.lib.fhe_d2d(self.ring.be.h, c.dptr, self.dptr, self.nwords * 8, self.stream))
+        return c
+
+    # -- checks as in dcrtpoly.h:164-173,186-194 ------------------------------------------------
+    def _check(self, rhs, what, need_eval=False):
+        if need_eval and (self.format != EVALUATION or rhs.format != EVALUATION):
+            raise RuntimeError(f"{what}: operator* for DCRTPolyImpl supported only in Format::EVALUATION")
+        if self.ring.n != rhs.ring.n:
+            raise RuntimeError(f"{what}: ring dimension mismatch")
+        if self.format != rhs.format:
+            raise RuntimeError(f"{what}: format mismatch")
+        if self.ring.towers != rhs.ring.towers:
+            raise RuntimeError(f"{what}: tower size mismatch")
+        if self.ring.q[0] != rhs.ring.q[0]:
+            raise RuntimeError(f"{what}: modulus mismatch")
+        if self.batch != rhs.batch:
+            raise RuntimeError(f"{what}: batch mismatch")
+
+    def _binary(self, rhs, op, what, need_eval=False):
+        self._check(rhs, what, need_eval)
+        out = DCRTPolyBatch(self.ring, self.batch, self.format, stream=self.stream)
+        self.ring.op(op, out.dptr, self.dptr, rhs.dptr, self.batch, self.stream)
+        return out
+
+    def _inplace(self, rhs, op):
+        # operator+= / -= / *= do no checks in the reference (dcrtpoly-impl.h:410-416, dcrtpoly.h:142-148)
+        self.ring.op(op, self.dptr, self.dptr, rhs.dptr, self.batch, self.stream)
+        return self
+
+    def Plus(self, rhs):
+        return self._binary(rhs, N.OP_ADD, "DCRTPolyImpl::Plus")
+
+    def Minus(self, rhs):
+        return self._binary(rhs, N.OP_SUB, "DCRTPolyImpl::Minus")
+
+    def Times(self, rhs):
+        return self._binary(rhs, N.OP_MUL, "DCRTPolyImpl::Times", need_eval=True)
+
+    __add__, __sub__, __mul__ = Plus, Minus, Times
+
+    def __iadd__(self, rhs):
+        return self._inplace(rhs, N.OP_ADD)
+
+    def __isub__(self, rhs):
+        return self._inplace(rhs, N.OP_SUB)
+
+    def __imul__(self, rhs):
+        return self._inplace(rhs, N.OP_MUL)
+
+    def SwitchFormat(self):
+        """dcrtpoly-impl.h:2518-2524: COEFFICIENT -> forward NTT, EVALUATION -> inverse."""
+        if self.format == COEFFICIENT:
+            self.ring.ntt(self.dptr, self.batch, inverse=False, stream=self.stream)
+            self.format = EVALUATION
+        else:
+            self.ring.ntt(self.dptr, self.batch, inverse=True, stream=self.stream)
+            self.format = COEFFICIENT
+
+    def SetFormat(self, fmt):
+        if self.format != fmt:
+            self.SwitchFormat()
