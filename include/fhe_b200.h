@@ -76,8 +76,7 @@ enum { FHE_KERNEL_BOOT = 0, FHE_KERNEL_MOD_ADD = 1, FHE_KERNEL_MOD_MULT = 2, FHE
 /* ---- runtime ------------------------------------------------------------------------------ */
 const char* fhe_last_error(void);
 const char* fhe_version(void);
-/* opts: "key=value,..."; keys: streams (default 4), arena_mb (initial arena slab, default 256),
- * staging_mb (pinned staging per direction for the *_host calls, default 64). */
+/* opts: "key=value,..."; keys: streams (default 4), arena_mb (arena slab size, default 256). */
 int fhe_init(int device, const char* opts, fhe_ctx** out);
 int fhe_shutdown(fhe_ctx* ctx);
 int fhe_device(const fhe_ctx* ctx);
@@ -147,6 +146,11 @@ int fhe_launch(fhe_ctx* ctx, int kernel_id, const void* desc, fhe_dptr heap_base
 /* dst = a (op) b with host buffers of batch*towers*N words each.  Streams the batch through the
  * device in chunks: pinned staging, H2D / kernel / D2H overlapped on separate streams. Blocking. */
 int fhe_dcrt_op_host(fhe_ring* ring, int op, uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t batch);
+/* Several ops on the SAME host operands with one upload: dsts[i] = a (ops[i]) b, i < nops <= 4.
+ * This is the PimData usage pattern of the reference (operands copied to the device once in the
+ * constructor, results fetched by sync(), pim/PimData.h:16-34) applied to a whole batch. Blocking. */
+int fhe_dcrt_multi_op_host(fhe_ring* ring, const int* ops, int nops, uint64_t* const* dsts,
+                           const uint64_t* a, const uint64_t* b, size_t batch);
 /* in-place transform of a host buffer (inverse = 0 forward, 1 inverse). Blocking. */
 int fhe_ntt_host(fhe_ring* ring, uint64_t* x, size_t batch, int inverse);
 

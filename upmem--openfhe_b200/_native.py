@@ -54,6 +54,7 @@ SIGNATURES = {
     "fhe_vec_op_scalar": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),
     "fhe_launch": (ci, [vp, ci, vp, u64]),
     "fhe_dcrt_op_host": (ci, [vp, ci, vp, vp, vp, sz]),
+    "fhe_dcrt_multi_op_host": (ci, [vp, ctypes.POINTER(ci), ci, ctypes.POINTER(vp), vp, vp, sz]),
     "fhe_ntt_host": (ci, [vp, vp, sz, ci]),
     "fhe_imad_probe": (ci, [vp, ci, ci, ci, ctypes.POINTER(ctypes.c_float)]),
 }

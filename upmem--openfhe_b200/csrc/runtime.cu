@@ -643,15 +643,28 @@ struct HostPipe {
 };
 }  // namespace
 
-extern "C" int fhe_dcrt_op_host(fhe_ring* r, int op, uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t batch) {
+extern "C" int fhe_dcrt_multi_op_host(fhe_ring* r, const int* ops, int nops, uint64_t* const* dsts,
+                                      const uint64_t* a, const uint64_t* b, size_t batch) {
     if (!r) return fail(FHE_EINVAL, "null ring");
-    if (op < FHE_OP_ADD || op > FHE_OP_MUL) return fail(FHE_EINVAL, "fhe_dcrt_op_host: unknown op %d", op);
+    if (!ops || !dsts || nops < 1 || nops > 4) return fail(FHE_EINVAL, "fhe_dcrt_multi_op_host: need 1..4 ops");
+    for (int i = 0; i < nops; i++) {
+        if (ops[i] < FHE_OP_ADD || ops[i] > FHE_OP_MUL) return fail(FHE_EINVAL, "fhe_dcrt_multi_op_host: unknown op %d", ops[i]);
+        if (!dsts[i]) return fail(FHE_EINVAL, "fhe_dcrt_multi_op_host: null destination");
+    }
     if (batch == 0) return FHE_OK;
-    if (!dst || !a || !b) return fail(FHE_EINVAL, "fhe_dcrt_op_host: null host pointer");
+    if (!a || !b) return fail(FHE_EINVAL, "fhe_dcrt_multi_op_host: null host pointer");
     CUDA_TRY(cudaSetDevice(r->ctx->device));
+    // slot = {a, b, result 1..nops-1}; the last op writes over a
     HostPipe hp(r, true);
     int rc = hp.reserve(batch, true);
     if (rc) return rc;
+    std::vector<void*> extra;
+    struct Guard { fhe_ring* r; std::vector<void*>& v; ~Guard() { for (void* p : v) r->ctx->arena.release(p); } } guard{r, extra};
+    for (size_t i = 0; i < hp.nslots * (size_t)(nops - 1); i++) {
+        void* p = nullptr;
+        if ((rc = r->ctx->arena.alloc(hp.chunk_items * hp.item_words * 8, &p))) return rc;
+        extra.push_back(p);
+    }
     size_t k = 0;
     for (size_t b0 = 0; b0 < batch; b0 += hp.chunk_items, k++) {
         size_t items = std::min(hp.chunk_items, batch - b0), words = items * hp.item_words;
@@ -661,11 +674,19 @@ extern "C" int fhe_dcrt_op_host(fhe_ring* r, int op, uint64_t* dst, const uint64
         uint64_t* db = (uint64_t*)hp.bufB[slot];
         CUDA_TRY(cudaMemcpyAsync(da, a + b0 * hp.item_words, words * 8, cudaMemcpyHostToDevice, s));
         CUDA_TRY(cudaMemcpyAsync(db, b + b0 * hp.item_words, words * 8, cudaMemcpyHostToDevice, s));
-        CUDA_TRY(launch_elementwise(r->dev, op, da, da, db, items, s));
-        CUDA_TRY(cudaMemcpyAsync(dst + b0 * hp.item_words, da, words * 8, cudaMemcpyDeviceToHost, s));
+        for (int i = 0; i < nops; i++) {
+            uint64_t* dd = (i == nops - 1) ? da : (uint64_t*)extra[slot * (nops - 1) + i];
+            CUDA_TRY(launch_elementwise(r->dev, ops[i], dd, da, db, items, s));
+            CUDA_TRY(cudaMemcpyAsync(dsts[i] + b0 * hp.item_words, dd, words * 8, cudaMemcpyDeviceToHost, s));
+        }
     }
     for (size_t i = 0; i < hp.nslots; i++) CUDA_TRY(cudaStreamSynchronize(r->ctx->streams[i]));
     return FHE_OK;
+}
+
+extern "C" int fhe_dcrt_op_host(fhe_ring* r, int op, uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t batch) {
+    uint64_t* d[1] = {dst};
+    return fhe_dcrt_multi_op_host(r, &op, 1, d, a, b, batch);
 }
 
 extern "C" int fhe_ntt_host(fhe_ring* r, uint64_t* x, size_t batch, int inverse) {

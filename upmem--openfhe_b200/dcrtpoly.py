@@ -152,6 +152,13 @@ class Ring:
     def op_host(self, op, dst, a, b, batch):
         N.check(N.lib.fhe_dcrt_op_host(self.h, op, _ptr(dst), _ptr(a), _ptr(b), batch))
 
+    def multi_op_host(self, ops, dsts, a, b, batch):
+        """dsts[i] = a (ops[i]) b with ONE upload of a and b (PimData residency pattern)."""
+        n = len(ops)
+        c_ops = (ctypes.c_int * n)(*ops)
+        c_dsts = (ctypes.c_void_p * n)(*[d.ctypes.data for d in dsts])
+        N.check(N.lib.fhe_dcrt_multi_op_host(self.h, c_ops, n, c_dsts, _ptr(a), _ptr(b), batch))
+
     def ntt_host(self, x, batch, inverse=False):
         N.check(N.lib.fhe_ntt_host(self.h, _ptr(x), batch, 1 if inverse else 0))
 
