@@ -1,0 +1,80 @@
+// int_probe.cu — integer-pipe throughput micro-benchmarks for the NTT roofline (SURVEY §8(d) asks the
+// builder to measure the integer peak on the box).  Each kernel runs ILP independent dependency chains
+// of one instruction flavour per thread; the host prints warp-level G-instructions/s per flavour.
+//   build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/bin/int_probe tools/int_probe.cu
+#include <cstdio>
+#include <cstdlib>
+#include <cuda_runtime.h>
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+constexpr int ILP = 8;
+
+enum { K_MADLO, K_MADWIDE, K_MADHI, K_MULHI64, K_MULLO64, K_SHOUP, K_SHOUP_APPROX, K_IADD3, K_COUNT };
+static const char* names[] = {"mad.lo.u32", "mad.wide.u32", "mad.hi.u32", "__umul64hi", "mul.lo.u64 (+add)",
+                              "shoup_lazy (mulhi64 + 2 mullo64)", "shoup_approx (3-product hi)", "add.u32 x3 (alu)"};
+
+template <int K>
+__global__ void __launch_bounds__(256) probe(u64* out, int iters, u32 seed) {
+    u32 a[ILP], b = seed | 1u, c = seed * 3u + threadIdx.x;
+    u64 x[ILP], w = 0x9E3779B97F4A7C15ull * (seed | 1u), wp = w ^ 0x5555555555555555ull, nq = 0ull - (w >> 4);
+#pragma unroll
+    for (int k = 0; k < ILP; k++) { a[k] = threadIdx.x * 2654435761u + k + blockIdx.x; x[k] = ((u64)a[k] << 32) | (a[k] * 77u + k); }
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int k = 0; k < ILP; k++) {
+            if (K == K_MADLO) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[k]) : "r"(b), "r"(c));
+            if (K == K_MADWIDE) x[k] = (u64)(u32)(x[k] >> 32) * (u64)b + x[k];
+            if (K == K_MADHI) asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(a[k]) : "r"(b), "r"(c));
+            if (K == K_MULHI64) x[k] = __umul64hi(x[k], w) + 1;
+            if (K == K_MULLO64) x[k] = x[k] * w + wp;
+            if (K == K_SHOUP) { u64 qh = __umul64hi(x[k], wp); x[k] = x[k] * w + qh * nq; }
+            if (K == K_SHOUP_APPROX) {
+                u32 y0 = (u32)x[k], y1 = (u32)(x[k] >> 32), p0 = (u32)wp, p1 = (u32)(wp >> 32);
+                u64 qh = (u64)y1 * p1 + __umulhi(y1, p0) + __umulhi(y0, p1);
+                x[k] = x[k] * w + qh * nq;
+            }
+            if (K == K_IADD3) asm volatile("add.u32 %0, %0, %1; add.u32 %0, %0, %2; add.u32 %0, %0, %1;" : "+r"(a[k]) : "r"(b), "r"(c));
+        }
+    }
+    u64 s = 0;
+#pragma unroll
+    for (int k = 0; k < ILP; k++) s ^= x[k] ^ a[k];
+    if (s == 0x1234567ull) out[0] = s;
+}
+
+template <int K>
+static void run(u64* d, int blocks, int iters) {
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    probe<K><<<blocks, 256>>>(d, 64, 12345u);
+    cudaDeviceSynchronize();
+    float best = 1e30f;
+    for (int r = 0; r < 5; r++) {
+        cudaEventRecord(e0);
+        probe<K><<<blocks, 256>>>(d, iters, 12345u + r);
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        if (ms < best) best = ms;
+    }
+    double ops = (double)blocks * 256 * iters * ILP;
+    printf("{\"probe\": \"%s\", \"ms\": %.4f, \"thread_ops_per_s\": %.4e, \"per_sm_per_clk_at_1965MHz\": %.2f}\n", names[K], best,
+           ops / (best * 1e-3), ops / (best * 1e-3) / 148 / 1.965e9);
+}
+
+int main(int argc, char** argv) {
+    int blocks = 148 * 8, iters = argc > 1 ? atoi(argv[1]) : 8192;
+    u64* d; cudaMalloc(&d, 256);
+    run<K_MADLO>(d, blocks, iters);
+    run<K_MADWIDE>(d, blocks, iters);
+    run<K_MADHI>(d, blocks, iters);
+    run<K_MULHI64>(d, blocks, iters);
+    run<K_MULLO64>(d, blocks, iters);
+    run<K_SHOUP>(d, blocks, iters);
+    run<K_SHOUP_APPROX>(d, blocks, iters);
+    run<K_IADD3>(d, blocks, iters);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { printf("cuda error %s\n", cudaGetErrorString(e)); return 1; }
+    return 0;
+}
