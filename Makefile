@@ -6,7 +6,7 @@ PKG     := upmem--openfhe_b200
 CSRC    := $(PKG)/csrc
 LIBDIR  := $(PKG)/lib
 NVFLAGS := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Iinclude -I$(CSRC)
-CU      := $(CSRC)/elementwise.cu $(CSRC)/ntt.cu $(CSRC)/runtime.cu
+CU      := $(CSRC)/elementwise.cu $(CSRC)/ntt.cu $(CSRC)/modops.cu $(CSRC)/runtime.cu
 OBJ     := $(patsubst $(CSRC)/%.cu,$(LIBDIR)/obj/%.o,$(CU))
 HDR     := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h include/pim/*.h)
 
@@ -22,7 +22,11 @@ oracle:
 	$(MAKE) -C oracle oracle
 ref:
 	$(MAKE) -C oracle ref
-host:
-	@true
+# C++ parity test of the include/pim surface (links the product .so and, as its checker, the oracle)
+host: lib oracle tests/cpp/bin/pim_surface_test
+tests/cpp/bin/pim_surface_test: tests/cpp/pim_surface_test.cpp $(HDR)
+	@mkdir -p $(dir $@)
+	g++ -std=c++17 -O2 -Wall -Iinclude -Ioracle $< -o $@ -L$(LIBDIR) -lfhe_b200 -Loracle -lfhe_oracle \
+	    -Wl,-rpath,'$$ORIGIN/../../../$(LIBDIR)' -Wl,-rpath,'$$ORIGIN/../../../oracle'
 clean:
 	rm -rf $(LIBDIR) && $(MAKE) -C oracle clean

@@ -136,9 +136,18 @@ int fhe_vec_op(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, fhe_dptr b, size_
 int fhe_vec_op_scalar(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, uint64_t scalar, size_t n,
                       uint64_t q, int stream);
 
+/* mod-ops of the PimData surface (pim/PimData.h:174-233): kind is `enum mod_kernel` of pim/common.h,
+ * `mod` the vector's current modulus; p / q as PimData::do_mod_ops passes them (new modulus,
+ * exponent, numerator or divisor in p; denominator in q).  Values follow OpenFHE's CPU NativeVector
+ * methods (mubintvecnat.cpp:111-195, 370-487).  dst may alias src.  MODINVERSE(EQ) blocks and
+ * returns FHE_EINVAL when an element has no inverse (the reference throws math_error). */
+int fhe_vec_modop(fhe_ctx* ctx, int kind, fhe_dptr dst, fhe_dptr src, size_t n, uint64_t mod, uint64_t p,
+                  uint64_t q, int stream);
+
 /* ---- legacy descriptor path ------------------------------------------------------------------ */
 /* desc points to a `struct mod_add_sub_mult` (pim/common.h:23-30) whose operands are byte offsets
- * from `heap_base` and byte sizes; kernel_id picks add / sub / mult.  Blocking, like
+ * from `heap_base` and byte sizes; kernel_id picks add / sub / mult; for FHE_KERNEL_MOD_OPS desc
+ * points to a `struct mod_ops` (pim/common.h:48-55).  Blocking, like
  * PimManager::start_kernel (DPU_SYNCHRONOUS, PimManager.h:68). */
 int fhe_launch(fhe_ctx* ctx, int kernel_id, const void* desc, fhe_dptr heap_base);
 

@@ -1,0 +1,156 @@
+/*
+ * pim/PimDCRTPoly.h — device-resident batch of DCRTPolys with the operator surface of the
+ * reference's DCRTPolyImpl on this path.  New header (the fork has no counterpart: its hook sits
+ * one level lower, NativeVectorT::ModAddEq, mubintvecnat.cpp:250-259); it is what
+ * DCRTPolyImpl::{Plus,Minus,Times,+=,-=,*=,SwitchFormat} dispatch to when a PimManager handle is
+ * attached, one CUDA launch for all towers of all polynomials of the batch.
+ *
+ * Mirrors, with the same checks and the same exception kinds (OPENFHE_THROW(math_error /
+ * not_implemented_error) become pim_math_error / pim_not_implemented_error):
+ *   Plus / Minus / Times            lattice/hal/default/dcrtpoly.h:164-200, dcrtpoly-impl.h:398-407
+ *   operator+= -= *= (no checks)    dcrtpoly-impl.h:410-416, 438-444, dcrtpoly.h:142-148
+ *   SwitchFormat / SetFormat        dcrtpoly-impl.h:2518-2524, lattice/ilelement.h:448-451
+ * Layout in HBM: [batch][tower][N] uint64.  Header only; link with libfhe_b200.so.
+ */
+#ifndef _PIM_DCRT_POLY_
+#define _PIM_DCRT_POLY_
+
+#include "PimManager.h"
+
+#include <cstdint>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+struct pim_math_error : std::runtime_error { using std::runtime_error::runtime_error; };
+struct pim_not_implemented_error : std::runtime_error { using std::runtime_error::runtime_error; };
+
+enum PimFormat { PIM_EVALUATION = 0, PIM_COEFFICIENT = 1 };   /* lbcrypto::Format values */
+
+/* ILDCRTParams on the device: ring dimension, moduli, roots, twiddle tables (fhe_ring). */
+class PimRing {
+public:
+  PimRing(PimManager *pim, uint32_t N, const std::vector<uint64_t> &q, const std::vector<uint64_t> &psi)
+      : pim_(pim), n_(N), q_(q), psi_(psi) {
+    if (!psi.empty() && psi.size() != q.size()) throw pim_math_error("PimRing: one root of unity per modulus");
+    PimManager::check(fhe_ring_create(pim->context(), N, (uint32_t)q.size(), q_.data(),
+                                      psi_.empty() ? nullptr : psi_.data(), &ring_), "PimRing");
+  }
+  ~PimRing() { fhe_ring_destroy(ring_); }
+  PimRing(const PimRing &) = delete;
+  PimRing &operator=(const PimRing &) = delete;
+
+  /* the benchmark's recipe: poly-benchmark-16k.cpp:82-101 */
+  static std::shared_ptr<PimRing> Generate(PimManager *pim, uint32_t nbits, uint32_t N, uint32_t towers) {
+    std::vector<uint64_t> q(towers), psi(towers);
+    PimManager::check(fhe_gen_params(nbits, N, towers, q.data(), psi.data()), "PimRing::Generate");
+    return std::make_shared<PimRing>(pim, N, q, psi);
+  }
+
+  uint32_t GetRingDimension() const { return n_; }
+  size_t GetNumTowers() const { return q_.size(); }
+  const std::vector<uint64_t> &GetModuli() const { return q_; }
+  const std::vector<uint64_t> &GetRoots() const { return psi_; }
+  fhe_ring *handle() const { return ring_; }
+  PimManager *manager() const { return pim_; }
+
+private:
+  PimManager *pim_;
+  uint32_t n_;
+  std::vector<uint64_t> q_, psi_;
+  fhe_ring *ring_ = nullptr;
+};
+
+class PimDCRTPoly {
+public:
+  PimDCRTPoly(std::shared_ptr<PimRing> ring, size_t batch, PimFormat format, const uint64_t *host = nullptr,
+              int stream = 0)
+      : ring_(std::move(ring)), batch_(batch), format_(format), stream_(stream) {
+    PimManager::check(fhe_alloc(ctx(), bytes() ? bytes() : 8, &d_), "PimDCRTPoly");
+    if (host) {
+      PimManager::check(fhe_h2d(ctx(), d_, host, bytes(), stream_), "PimDCRTPoly upload");
+      PimManager::check(fhe_sync(ctx(), stream_), "PimDCRTPoly upload");
+    }
+  }
+  PimDCRTPoly(const PimDCRTPoly &o) : PimDCRTPoly(o.ring_, o.batch_, o.format_, nullptr, o.stream_) {
+    PimManager::check(fhe_d2d(ctx(), d_, o.d_, bytes(), stream_), "PimDCRTPoly copy");
+  }
+  PimDCRTPoly(PimDCRTPoly &&o) noexcept
+      : ring_(std::move(o.ring_)), batch_(o.batch_), format_(o.format_), stream_(o.stream_), d_(o.d_) { o.d_ = 0; }
+  PimDCRTPoly &operator=(PimDCRTPoly o) {
+    std::swap(ring_, o.ring_); std::swap(batch_, o.batch_); std::swap(format_, o.format_);
+    std::swap(stream_, o.stream_); std::swap(d_, o.d_);
+    return *this;
+  }
+  ~PimDCRTPoly() { if (d_ && ring_) fhe_free(ctx(), d_); }
+
+  PimFormat GetFormat() const { return format_; }
+  size_t GetBatch() const { return batch_; }
+  size_t words() const { return batch_ * ring_->GetNumTowers() * ring_->GetRingDimension(); }
+  size_t bytes() const { return words() * sizeof(uint64_t); }
+  fhe_dptr device_ptr() const { return d_; }
+  const std::shared_ptr<PimRing> &GetParams() const { return ring_; }
+
+  /* device -> host, blocking (the PimData::sync of this handle) */
+  void sync(uint64_t *out) const {
+    PimManager::check(fhe_d2h(ctx(), out, d_, bytes(), stream_), "PimDCRTPoly::sync");
+    PimManager::check(fhe_sync(ctx(), stream_), "PimDCRTPoly::sync");
+  }
+  std::vector<uint64_t> GetValues() const { std::vector<uint64_t> v(words()); sync(v.data()); return v; }
+
+  PimDCRTPoly Plus(const PimDCRTPoly &rhs) const { check(rhs, "add", false); return binary(rhs, FHE_OP_ADD); }
+  PimDCRTPoly Minus(const PimDCRTPoly &rhs) const { check(rhs, "subtract", false); return binary(rhs, FHE_OP_SUB); }
+  PimDCRTPoly Times(const PimDCRTPoly &rhs) const { check(rhs, "multiply", true); return binary(rhs, FHE_OP_MUL); }
+  PimDCRTPoly operator+(const PimDCRTPoly &rhs) const { return Plus(rhs); }
+  PimDCRTPoly operator-(const PimDCRTPoly &rhs) const { return Minus(rhs); }
+  PimDCRTPoly operator*(const PimDCRTPoly &rhs) const { return Times(rhs); }
+  PimDCRTPoly &operator+=(const PimDCRTPoly &rhs) { return inplace(rhs, FHE_OP_ADD); }
+  PimDCRTPoly &operator-=(const PimDCRTPoly &rhs) { return inplace(rhs, FHE_OP_SUB); }
+  PimDCRTPoly &operator*=(const PimDCRTPoly &rhs) { return inplace(rhs, FHE_OP_MUL); }
+
+  void SwitchFormat() {
+    if (format_ == PIM_COEFFICIENT) {
+      PimManager::check(fhe_ntt_forward(ring_->handle(), d_, batch_, stream_), "SwitchFormat");
+      format_ = PIM_EVALUATION;
+    } else {
+      PimManager::check(fhe_ntt_inverse(ring_->handle(), d_, batch_, stream_), "SwitchFormat");
+      format_ = PIM_COEFFICIENT;
+    }
+  }
+  void SetFormat(PimFormat f) { if (format_ != f) SwitchFormat(); }
+
+private:
+  fhe_ctx *ctx() const { return ring_->manager()->context(); }
+
+  void check(const PimDCRTPoly &rhs, const char *verb, bool need_eval) const {
+    if (ring_->GetRingDimension() != rhs.ring_->GetRingDimension()) throw pim_math_error("RingDimension missmatch");
+    if (need_eval) {
+      if (format_ != PIM_EVALUATION || rhs.format_ != PIM_EVALUATION)
+        throw pim_not_implemented_error("operator* for DCRTPolyImpl supported only in Format::EVALUATION");
+    } else if (format_ != rhs.format_) {
+      throw pim_not_implemented_error("Format missmatch");
+    }
+    if (ring_->GetNumTowers() != rhs.ring_->GetNumTowers())
+      throw pim_math_error(std::string("tower size mismatch; cannot ") + verb);
+    if (ring_->GetModuli()[0] != rhs.ring_->GetModuli()[0]) throw pim_math_error("Modulus missmatch");
+    if (batch_ != rhs.batch_) throw pim_math_error("batch size mismatch");
+  }
+  PimDCRTPoly binary(const PimDCRTPoly &rhs, int op) const {
+    PimDCRTPoly out(ring_, batch_, format_, nullptr, stream_);
+    PimManager::check(fhe_dcrt_op(ring_->handle(), op, out.d_, d_, rhs.d_, batch_, stream_), "DCRTPoly op");
+    return out;
+  }
+  PimDCRTPoly &inplace(const PimDCRTPoly &rhs, int op) {
+    PimManager::check(fhe_dcrt_op(ring_->handle(), op, d_, d_, rhs.d_, batch_, stream_), "DCRTPoly op");
+    return *this;
+  }
+
+  std::shared_ptr<PimRing> ring_;
+  size_t batch_;
+  PimFormat format_;
+  int stream_;
+  fhe_dptr d_ = 0;
+};
+
+#endif /* _PIM_DCRT_POLY_ */

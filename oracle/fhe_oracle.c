@@ -183,6 +183,102 @@ void orc_vec_modmul_scalar(uint64_t* dst, const uint64_t* a, uint64_t s, size_t 
     for (size_t i = 0; i < n; i++) dst[i] = orc_modmul_barrett(a[i], s, q, mu);
 }
 
+/* ---- mod-ops of the PimData surface (pim/PimData.h:174-233 -> mod_kernel, pim/common.h:32-46).
+ * CPU definitions: NativeVectorT::SwitchModulus / Mod / ModEq  mubintvecnat.cpp:111-195,
+ * ModByTwo(Eq) :370-385, ModExp(Eq) :387-410, ModInverse(Eq) mubintvecnat.h:546-566,
+ * MultiplyAndRound(Eq) :423-455, DivideAndRound(Eq) :457-487; scalars ubintnat.h:536-541,
+ * 596-606, 1507-1530, 1565-1592.  kind is enum mod_kernel; the Eq and non-Eq forms compute the
+ * same values.  Returns 0, or 1 when ModInverse meets an element without an inverse (the
+ * reference throws math_error there) or a divisor is zero. */
+static uint64_t modexp_ref(uint64_t v, uint64_t b, uint64_t m) {   /* ubintnat.h:1507-1530 */
+    u128 t = v, pw = b, mm = m, r = 1;
+    if (pw & 1) { r = r * t; if (r >= mm) r %= mm; }
+    while (pw >>= 1) {
+        t = t * t; if (t >= mm) t %= mm;
+        if (pw & 1) { r = r * t; if (r >= mm) r %= mm; }
+    }
+    return (uint64_t)r;
+}
+static int modinverse_ref(uint64_t v, uint64_t m, uint64_t* out) {   /* ubintnat.h:1565-1592 */
+    int64_t modulus = (int64_t)m, a = (int64_t)(v % m);
+    if (a == 0) return 1;
+    if (modulus == 1) { *out = 0; return 0; }
+    int64_t y = 0, x = 1;
+    while (a > 1) {
+        int64_t t = modulus, qq = a / t;
+        modulus = a % t; a = t; t = y;
+        y = x - qq * y; x = t;
+    }
+    if (x < 0) x += (int64_t)m;
+    *out = (uint64_t)x;
+    return 0;
+}
+static uint64_t mulround_ref(uint64_t v, uint64_t p, uint64_t q) {    /* ubintnat.h:536-541 */
+    volatile double ratio = (double)v / (double)q;       /* volatile: no fused multiply-add */
+    volatile double prod = (double)p * ratio;
+    return (uint64_t)(prod + 0.5);
+}
+static uint64_t divround_ref(uint64_t v, uint64_t q) {               /* ubintnat.h:596-606 */
+    uint64_t ans = v / q, rem = v % q;
+    return rem > (q >> 1) ? ans + 1 : ans;
+}
+int orc_vec_modop(int kind, uint64_t* dst, const uint64_t* src, size_t n, uint64_t mod, uint64_t p, uint64_t q) {
+    uint64_t half = mod >> 1;
+    int bad = 0;
+    switch (kind) {
+    case 1: case 2:                                   /* MOD_NORMAL, MODEQ: nm == 2 -> ModByTwo */
+        if (p == 2) { for (size_t i = 0; i < n; i++) dst[i] = 1 & (src[i] ^ (uint64_t)(src[i] > half)); return 0; }
+        /* fall through */
+    case 0: {                                         /* SWITCHMODULUS */
+        uint64_t om = mod, nm = p;
+        if (nm == 0) return 1;
+        if (nm > om) {
+            uint64_t diff = nm - om;
+            for (size_t i = 0; i < n; i++) { uint64_t v = src[i]; if (v > half) v += diff; dst[i] = v; }
+        } else {
+            uint64_t diff = nm - (om % nm);
+            for (size_t i = 0; i < n; i++) {
+                uint64_t v = src[i];
+                if (v > half) v += diff;
+                if (v >= nm) v %= nm;
+                dst[i] = v;
+            }
+        }
+        return 0;
+    }
+    case 3: case 4:                                   /* MODBYTWO(EQ) */
+        for (size_t i = 0; i < n; i++) dst[i] = 1 & (src[i] ^ (uint64_t)(src[i] > half));
+        return 0;
+    case 5: case 6: {                                 /* MODEXP(EQ): exponent reduced mod the modulus */
+        if (mod == 0) return 1;
+        uint64_t b = p >= mod ? p % mod : p;
+        for (size_t i = 0; i < n; i++) dst[i] = modexp_ref(src[i], b, mod);
+        return 0;
+    }
+    case 7: case 8:                                   /* MODINVERSE(EQ) */
+        if (mod == 0) return 1;
+        for (size_t i = 0; i < n; i++) { uint64_t r = 0; bad |= modinverse_ref(src[i], mod, &r); dst[i] = r; }
+        return bad;
+    case 9: case 10:                                  /* MULTIPLYANDROUND(EQ) */
+        if (q == 0 || mod == 0) return 1;
+        for (size_t i = 0; i < n; i++) {
+            uint64_t v = src[i];
+            if (v > half) dst[i] = mod - mulround_ref(mod - v, p, q);
+            else dst[i] = mulround_ref(v, p, q) % mod;
+        }
+        return 0;
+    case 11: case 12:                                 /* DIVIDEANDROUND(EQ): divisor travels in p */
+        if (p == 0) return 1;
+        for (size_t i = 0; i < n; i++) {
+            uint64_t v = src[i];
+            if (v > half) dst[i] = mod - divround_ref(mod - v, p);
+            else dst[i] = divround_ref(v, p);
+        }
+        return 0;
+    }
+    return 1;
+}
+
 /* lbcrypto::ReverseBits(i, msb) */
 static uint32_t bitrev(uint32_t x, uint32_t bits) {
     uint32_t r = 0;

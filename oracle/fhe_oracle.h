@@ -52,6 +52,10 @@ void orc_vec_modadd_scalar(uint64_t* dst, const uint64_t* a, uint64_t s, size_t 
 void orc_vec_modsub_scalar(uint64_t* dst, const uint64_t* a, uint64_t s, size_t n, uint64_t q);
 void orc_vec_modmul_scalar(uint64_t* dst, const uint64_t* a, uint64_t s, size_t n, uint64_t q);
 
+/* mod-ops of the PimData surface; kind = enum mod_kernel (pim/common.h:32-46); 0 ok, 1 = the
+ * reference would throw (no inverse / zero divisor) */
+int orc_vec_modop(int kind, uint64_t* dst, const uint64_t* src, size_t n, uint64_t mod, uint64_t p, uint64_t q);
+
 /* ---- twiddle tables (transformnat-impl.h:708-763) ----
  * W[bitrev(i)] = psi^i, WI[bitrev(i)] = psi^-i (i < N), Wp/WIp their Shoup companions,
  * *ninv = N^-1 mod q and *ninvp its companion (TableCOI[log2 N]). */

@@ -148,6 +148,31 @@ ref_polys* ref_polys_binary(const ref_polys* a, const ref_polys* b, int op) {
     return r;
 }
 
+// mod-ops of the PimData surface executed by the reference's own NativeVector (in-place forms:
+// mubintvecnat.cpp:111-195,370-487, mubintvecnat.h:560-566).  kind = enum mod_kernel.
+// Returns 0, or 1 if the reference threw.
+int ref_vec_modop(int kind, uint64_t* data, size_t n, uint64_t mod, uint64_t p, uint64_t q) {
+    try {
+        NativeVector v(n, NativeInteger(mod));
+        for (size_t i = 0; i < n; i++) v[i] = NativeInteger(data[i]);
+        switch (kind) {
+            case 0: v.SwitchModulus(NativeInteger(p)); break;
+            case 1: case 2: v.ModEq(NativeInteger(p)); break;
+            case 3: case 4: v.ModByTwoEq(); break;
+            case 5: case 6: v.ModExpEq(NativeInteger(p)); break;
+            case 7: case 8: v.ModInverseEq(); break;
+            case 9: case 10: v.MultiplyAndRoundEq(NativeInteger(p), NativeInteger(q)); break;
+            case 11: case 12: v.DivideAndRoundEq(NativeInteger(p)); break;
+            default: return 1;
+        }
+        for (size_t i = 0; i < n; i++) data[i] = v[i].ConvertToInt();
+        return 0;
+    }
+    catch (...) {
+        return 1;
+    }
+}
+
 int ref_max_threads(void) { return omp_get_max_threads(); }
 
 }  // extern "C"

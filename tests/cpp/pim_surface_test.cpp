@@ -1,0 +1,161 @@
+// pim_surface_test.cpp — C++ parity test of the kept intercept surface (include/pim/*.h) on a B200.
+// Calls PimData / PimManager / PimDCRTPoly exactly like code written against the UPMEM fork would
+// (src/pke/examples/simple-integers.cpp:120-130 shows the intended use) and checks every result
+// against the CPU oracle (oracle/fhe_oracle.h, test infrastructure) — bit exact.
+#include "pim/PimData.h"
+#include "pim/PimDCRTPoly.h"
+
+#include "fhe_oracle.h"
+
+#include <cstdio>
+#include <cstdlib>
+#include <random>
+#include <vector>
+
+static int failures = 0;
+#define EXPECT(cond, ...)                                                  \
+    do {                                                                   \
+        if (!(cond)) { failures++; printf("FAIL %s:%d ", __FILE__, __LINE__); printf(__VA_ARGS__); printf("\n"); } \
+    } while (0)
+
+static std::vector<uint64_t> rnd(size_t n, uint64_t q, uint64_t seed) {
+    std::vector<uint64_t> v(n);
+    orc_fill_uniform(v.data(), n, q, seed, 0);
+    return v;
+}
+
+static void test_pimdata_kat() {
+    // UnitTestDCRTElements.cpp:285-406 values through the PimData operators, q = 8353
+    PimData a{2, 4, 3, 2}, b{2, 1, 2, 0};
+    const uint64_t q = 8353;
+    PimData s = a.ModAdd(b, q), d = a.ModSub(b, q), m = a.ModMul(b, q);
+    s.sync(); d.sync(); m.sync();
+    EXPECT((s.host() == std::vector<uint64_t>{4, 5, 5, 2}), "ModAdd");
+    EXPECT((d.host() == std::vector<uint64_t>{0, 3, 1, 2}), "ModSub");
+    EXPECT((m.host() == std::vector<uint64_t>{4, 4, 6, 0}), "ModMul");
+    PimData c = a;                 // shallow, shared block: must not double free (reference bug)
+    c.ModAddEq(b, q);
+    a.sync();
+    EXPECT((a.host() == std::vector<uint64_t>{4, 5, 5, 2}), "shared block after ModAddEq");
+    PimData w = a + b;             // default modulus 2^64-1: plain wrapping add
+    w.sync();
+    EXPECT((w.host() == std::vector<uint64_t>{6, 6, 7, 2}), "operator+ default modulus");
+    PimData e;                     // default-constructed handle is destructible
+}
+
+static void test_pimdata_random(uint64_t q, size_t n) {
+    std::vector<uint64_t> ha = rnd(n, q, 11), hb = rnd(n, q, 12), exp(n);
+    PimData a(ha), b(hb);
+    const uint64_t scalar = 0x123456789abcdefull;
+    struct { int op; void (*vec)(uint64_t*, const uint64_t*, const uint64_t*, size_t, uint64_t);
+             void (*sc)(uint64_t*, const uint64_t*, uint64_t, size_t, uint64_t); } ops[3] = {
+        {0, orc_vec_modadd, orc_vec_modadd_scalar}, {1, orc_vec_modsub, orc_vec_modsub_scalar},
+        {2, orc_vec_modmul, orc_vec_modmul_scalar}};
+    for (auto& o : ops) {
+        PimData r = o.op == 0 ? a.ModAdd(b, q) : o.op == 1 ? a.ModSub(b, q) : a.ModMul(b, q);
+        r.sync();
+        o.vec(exp.data(), ha.data(), hb.data(), n, q);
+        EXPECT(r.host() == exp, "vector op %d q=%llu n=%zu", o.op, (unsigned long long)q, n);
+        PimData rs = o.op == 0 ? a.ModAdd(scalar, q) : o.op == 1 ? a.ModSub(scalar, q) : a.ModMul(scalar, q);
+        rs.sync();
+        o.sc(exp.data(), ha.data(), scalar, n, q);
+        EXPECT(rs.host() == exp, "scalar op %d q=%llu n=%zu", o.op, (unsigned long long)q, n);
+        PimData t(ha);             // in-place forms
+        if (o.op == 0) t.ModAddEq(b, q); else if (o.op == 1) t.ModSubEq(b, q); else t.ModMulEq(b, q);
+        t.sync();
+        o.vec(exp.data(), ha.data(), hb.data(), n, q);
+        EXPECT(t.host() == exp, "vector_eq op %d", o.op);
+    }
+}
+
+static void test_pimdata_modops(uint64_t mod, size_t n) {
+    // pim/PimData.h:174-233 of the reference: Mod / switchmod / ModByTwo / ModExp / ModInverse /
+    // MultiplyAndRound / DivideAndRound, through the mod_ops descriptor and ELEM_MOD_OPS
+    std::vector<uint64_t> hx = rnd(n, mod, 21), exp(n);
+    for (auto& v : hx) if (v == 0) v = 1;
+    hx[0] = mod - 1; hx[1] = mod >> 1; hx[2] = (mod >> 1) + 1;
+    auto expect = [&](int kind, uint64_t p, uint64_t q) {
+        int rc = orc_vec_modop(kind, exp.data(), hx.data(), n, mod, p, q);
+        EXPECT(rc == 0, "oracle modop %d", kind);
+    };
+    PimData x(hx);
+    { PimData r = x.Mod(mod, mod / 3 + 2); r.sync(); expect(MOD_NORMAL, mod / 3 + 2, 0); EXPECT(r.host() == exp, "Mod"); }
+    { PimData r = x.ModByTwo(mod); r.sync(); expect(MODBYTWO, 0, 0); EXPECT(r.host() == exp, "ModByTwo"); }
+    { PimData r = x.ModExp(mod, 65537); r.sync(); expect(MODEXP, 65537, 0); EXPECT(r.host() == exp, "ModExp"); }
+    { PimData r = x.ModInverse(mod); r.sync(); expect(MODINVERSE, 0, 0); EXPECT(r.host() == exp, "ModInverse"); }
+    { PimData r = x.MultiplyAndRound(mod, 12345, mod / 5 + 1); r.sync(); expect(MULTIPLYANDROUND, 12345, mod / 5 + 1); EXPECT(r.host() == exp, "MultiplyAndRound"); }
+    { PimData r = x.DivideAndRound(mod, 7); r.sync(); expect(DIVIDEANDROUND, 7, 0); EXPECT(r.host() == exp, "DivideAndRound"); }
+    { PimData t(hx); t.switchmod(mod, mod + 1000); t.sync(); expect(SWITCHMODULUS, mod + 1000, 0); EXPECT(t.host() == exp, "switchmod"); }
+    { PimData t(hx); t.ModEq(mod, 2); t.sync(); expect(MODEQ, 2, 0); EXPECT(t.host() == exp, "ModEq(2)"); }
+    { PimData t(hx); t.ModExpEq(mod, mod + 3); t.sync(); expect(MODEXPEQ, mod + 3, 0); EXPECT(t.host() == exp, "ModExpEq"); }
+    { PimData t(hx); t.DivideAndRoundEq(mod, mod / 9 + 1); t.sync(); expect(DIVIDEANDROUNDEQ, mod / 9 + 1, 0); EXPECT(t.host() == exp, "DivideAndRoundEq"); }
+    std::vector<uint64_t> hz = hx; hz[3] = 0;
+    PimData z(hz);
+    bool threw = false;
+    try { z.ModInverseEq(mod); } catch (const std::runtime_error&) { threw = true; }
+    EXPECT(threw, "ModInverse of 0 must throw (math_error in the reference)");
+}
+
+static void test_dcrtpoly(uint32_t N, uint32_t T, size_t B) {
+    PimManager* pim = PimManager::getPim(4);
+    auto ring = PimRing::Generate(pim, 60, N, T);
+    std::vector<uint64_t> q(T), psi(T);
+    orc_gen_dcrt_params(60, N, T, q.data(), psi.data());
+    EXPECT(q == ring->GetModuli() && psi == ring->GetRoots(), "parameter recipe N=%u", N);
+    orc_ctx* oc = orc_ctx_create(N, T, q.data(), psi.data());
+    size_t words = B * T * (size_t)N;
+    std::vector<uint64_t> ha(words), hb(words), exp(words);
+    for (size_t b = 0; b < B; b++)
+        for (uint32_t t = 0; t < T; t++) {
+            orc_fill_uniform(&ha[(b * T + t) * N], N, q[t], 5, (b * T + t) * (size_t)N);
+            orc_fill_uniform(&hb[(b * T + t) * N], N, q[t], 6, (b * T + t) * (size_t)N);
+        }
+    PimDCRTPoly a(ring, B, PIM_EVALUATION, ha.data()), b(ring, B, PIM_EVALUATION, hb.data());
+    for (int op = 0; op < 3; op++) {
+        PimDCRTPoly c = op == 0 ? a + b : op == 1 ? a - b : a * b;
+        orc_dcrt_elementwise(oc, op, exp.data(), ha.data(), hb.data(), B, 0);
+        EXPECT(c.GetValues() == exp, "DCRTPoly op %d N=%u", op, N);
+        PimDCRTPoly d(a);
+        if (op == 0) d += b; else if (op == 1) d -= b; else d *= b;
+        EXPECT(d.GetValues() == exp, "DCRTPoly in-place op %d N=%u", op, N);
+    }
+    PimDCRTPoly x(ring, B, PIM_COEFFICIENT, ha.data());
+    bool threw = false;
+    try { x.Times(x); } catch (const pim_not_implemented_error&) { threw = true; }
+    EXPECT(threw, "Times outside EVALUATION must throw");
+    threw = false;
+    try { x.Plus(a); } catch (const pim_not_implemented_error&) { threw = true; }
+    EXPECT(threw, "Plus with a format mismatch must throw");
+    x.SwitchFormat();
+    exp = ha;
+    orc_dcrt_ntt(oc, 0, exp.data(), B, 0);
+    EXPECT(x.GetFormat() == PIM_EVALUATION && x.GetValues() == exp, "forward NTT N=%u", N);
+    x.SwitchFormat();
+    EXPECT(x.GetFormat() == PIM_COEFFICIENT && x.GetValues() == ha, "round trip N=%u", N);
+    PimDCRTPoly y(ring, B, PIM_EVALUATION, hb.data());
+    y.SetFormat(PIM_COEFFICIENT);
+    exp = hb;
+    orc_dcrt_ntt(oc, 1, exp.data(), B, 0);
+    EXPECT(y.GetValues() == exp, "inverse NTT N=%u", N);
+    orc_ctx_destroy(oc);
+}
+
+int main() {
+    try {
+        test_pimdata_kat();
+        test_pimdata_random(73, 1000);
+        test_pimdata_random(1152921504606748673ull, 16384);
+        test_pimdata_random(8353, 3);
+        test_pimdata_modops(8353, 1000);
+        test_pimdata_modops(1152921504606748673ull, 4099);
+        test_dcrtpoly(1 << 14, 2, 2);      // BASELINE configs[0]
+        test_dcrtpoly(1 << 16, 3, 2);
+        test_dcrtpoly(1 << 11, 4, 3);
+    } catch (const std::exception& e) {
+        printf("FAIL exception: %s\n", e.what());
+        failures++;
+    }
+    PimManager::releasePim();
+    printf(failures ? "pim_surface_test: %d FAILURE(S)\n" : "pim_surface_test: all ok\n", failures);
+    return failures ? 1 : 0;
+}

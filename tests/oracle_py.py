@@ -39,6 +39,7 @@ class Oracle:
             ("orc_ctx_create", vp, [u32, u32, vp, vp]), ("orc_ctx_destroy", None, [vp]),
             ("orc_dcrt_elementwise", None, [vp, ci, vp, vp, vp, sz, ci]),
             ("orc_dcrt_ntt", None, [vp, ci, vp, sz, ci]), ("orc_max_threads", ci, []),
+            ("orc_vec_modop", ci, [ci, vp, vp, sz, u64, u64, u64]),
             ("orc_uniform_at", u64, [u64, u64, u64]), ("orc_fill_uniform", None, [vp, sz, u64, u64, u64]),
         ]:
             f = getattr(L, name)
@@ -82,6 +83,12 @@ class Oracle:
         f = [self.L.orc_vec_modadd_scalar, self.L.orc_vec_modsub_scalar, self.L.orc_vec_modmul_scalar][op]
         f(_p(out), _p(a), int(s), a.size, int(q))
         return out
+
+    def modop(self, kind, x, mod, p=0, q=0):
+        x = np.ascontiguousarray(x, np.uint64)
+        out = np.empty_like(x)
+        rc = self.L.orc_vec_modop(kind, _p(out), _p(x), x.size, int(mod), int(p), int(q))
+        return rc, out
 
     def ctx(self, n, q, psi):
         return OracleCtx(self, n, q, psi)

@@ -75,3 +75,15 @@ def test_product_does_not_link_the_oracle(pkg):
                 assert not banned.search(open(os.path.join(root, f)).read()), f
     sym = subprocess.run(["nm", "-D", pkg.LIB_PATH], capture_output=True, text=True).stdout
     assert " orc_" not in sym and " ref_" not in sym
+
+
+def test_cpp_surface_builds_and_fails_loudly_without_gpu():
+    """include/pim/*.h compile as C++17 against the C ABI; with no GPU the surface throws (no fallback)."""
+    import torch
+    subprocess.check_call(["make", "-C", ROOT, "host"], stdout=subprocess.DEVNULL)
+    exe = os.path.join(ROOT, "tests", "cpp", "bin", "pim_surface_test")
+    assert os.path.exists(exe)
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present: the binary is run by the gpu tests")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode != 0 and "no CPU fallback" in r.stdout

@@ -233,3 +233,54 @@ def test_fill_uniform_matches_oracle_generator(pkg, backend, oracle):
     assert np.array_equal(got, oracle.fill_ring(batch, n, q, 20260001))
     assert (got < q[None, :, None]).all()
     ring.close()
+
+
+# ---- mod-ops of the PimData surface -------------------------------------------
+@pytest.mark.parametrize("mod", [73, 8353, (1 << 40) + 15, 1152921504606748673, (1 << 63) + 29])
+def test_modops_vs_oracle(pkg, backend, oracle, mod):
+    n = 10007
+    rng = np.random.default_rng(mod % 1000)
+    x = rng.integers(0, mod, size=n, dtype=np.uint64)
+    x[:4] = [mod - 1, mod >> 1, (mod >> 1) + 1, 1]
+    dx, dy = backend.alloc(n * 8), backend.alloc(n * 8)
+    cases = [(0, mod + 1000, 0), (0, max(3, mod // 3), 0), (1, 2, 0), (2, max(5, mod // 7), 0), (3, 0, 0), (4, 0, 0),
+             (5, 65537, 0), (6, mod + 5, 0), (9, 12345, max(7, mod // 5)), (10, mod - 1, mod), (11, 7, 0),
+             (12, max(2, mod // 1000), 0)]
+    if mod >= (1 << 63):                       # new modulus above 2^64 is not representable; skip the growing switch
+        cases = cases[1:]
+    for kind, p, q in cases:
+        backend.h2d(dx, x)
+        rc, exp = oracle.modop(kind, x, mod, p, q)
+        assert rc == 0
+        backend.vec_modop(kind, dy, dx, n, mod, p, q)
+        assert np.array_equal(backend.d2h(dy, n), exp), f"kind {kind}"
+        backend.vec_modop(kind, dx, dx, n, mod, p, q)          # in place
+        assert np.array_equal(backend.d2h(dx, n), exp), f"kind {kind} in place"
+    if mod < (1 << 63):                        # ModInverse works on signed 64-bit values in the reference
+        xi = x.copy()
+        xi[xi == 0] = 1
+        if mod in (73, 8353, 1152921504606748673):               # prime: every non-zero element is invertible
+            backend.h2d(dx, xi)
+            rc, exp = oracle.modop(7, xi, mod)
+            assert rc == 0
+            backend.vec_modop(7, dy, dx, n, mod)
+            assert np.array_equal(backend.d2h(dy, n), exp)
+        xi[5] = 0
+        backend.h2d(dx, xi)
+        with pytest.raises(pkg.FheError):
+            backend.vec_modop(8, dx, dx, n, mod)
+    with pytest.raises(pkg.FheError):
+        backend.vec_modop(9, dy, dx, n, mod, 5, 0)             # divide by zero, as the reference throws
+    backend.free(dx); backend.free(dy)
+
+
+def test_cpp_pim_surface_binary():
+    """include/pim/{PimManager,PimData,PimDCRTPoly}.h driven from C++ (tests/cpp/pim_surface_test.cpp)."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "tests", "cpp", "bin", "pim_surface_test")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-C", root, "host"])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "all ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

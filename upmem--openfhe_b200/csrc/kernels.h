@@ -36,6 +36,10 @@ cudaError_t launch_ntt(const RingDev& r, uint64_t* data, size_t batch, bool inve
 // Counter-based uniform fill in [0, q_t) per tower (same definition as the test oracle's generator).
 cudaError_t launch_fill_uniform(const RingDev& r, uint64_t* dst, size_t batch, uint64_t seed,
                                 cudaStream_t st);
+// mod-ops of the PimData surface; kind = enum mod_kernel (pim/common.h).  *err (device int) is set to 1
+// when ModInverse meets an element without an inverse.
+cudaError_t launch_modop(int kind, uint64_t* dst, const uint64_t* src, size_t n, uint64_t mod, uint64_t p,
+                         uint64_t q, int* err, cudaStream_t st);
 // Integer-pipe probe: every thread runs `iters` dependent-chain-free 64x64->128 multiply-adds.
 cudaError_t launch_imad_probe(uint64_t* out, int blocks, int threads, int iters, cudaStream_t st);
 

@@ -139,6 +139,7 @@ struct fhe_ctx {
     std::mutex mu;
     std::map<int, Timer> timers;
     std::vector<void*> pinned;
+    int* d_err = nullptr;          // device flag written by kernels that can meet invalid elements
 };
 
 struct fhe_ring {
@@ -560,6 +561,44 @@ extern "C" int fhe_vec_op(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, fhe_dp
     return FHE_OK;
 }
 
+// kind = enum mod_kernel (pim/common.h:32-46).  Host-side argument handling as the reference's vector
+// methods do it: ModExp reduces the exponent mod the modulus first (mubintvecnat.cpp:391-392).
+extern "C" int fhe_vec_modop(fhe_ctx* ctx, int kind, fhe_dptr dst, fhe_dptr src, size_t n, uint64_t mod,
+                             uint64_t p, uint64_t q, int stream) {
+    cudaStream_t s;
+    int rc = get_stream(ctx, stream, &s);
+    if (rc) return rc;
+    if (kind < SWITCHMODULUS || kind > DIVIDEANDROUNDEQ) return fail(FHE_EINVAL, "fhe_vec_modop: unknown mod_kernel %d", kind);
+    if (mod == 0) return fail(FHE_EINVAL, "fhe_vec_modop: modulus is zero");
+    if (kind <= MODEQ && p == 0) return fail(FHE_EINVAL, "fhe_vec_modop: new modulus is zero");
+    if ((kind == MULTIPLYANDROUND || kind == MULTIPLYANDROUNDEQ) && q == 0)
+        return fail(FHE_EINVAL, "NativeIntegerT MultiplyAndRound: Divide by zero");
+    if ((kind == DIVIDEANDROUND || kind == DIVIDEANDROUNDEQ) && p == 0)
+        return fail(FHE_EINVAL, "NativeIntegerT DivideAndRound: zero");
+    if (n == 0) return FHE_OK;
+    if (!dst || !src) return fail(FHE_EINVAL, "fhe_vec_modop: null device pointer");
+    if ((kind == MODEXP || kind == MODEXPEQ) && p >= mod) p %= mod;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    bool inv = kind == MODINVERSE || kind == MODINVERSEEQ;
+    if (inv) {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        if (!ctx->d_err) {
+            void* e = nullptr;
+            if ((rc = ctx->arena.alloc(256, &e))) return rc;
+            ctx->d_err = (int*)e;
+        }
+    }
+    if (inv) CUDA_TRY(cudaMemsetAsync(ctx->d_err, 0, sizeof(int), s));
+    CUDA_TRY(launch_modop(kind, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, n, mod, p, q, ctx->d_err, s));
+    if (inv) {                                   // the reference throws math_error: report it synchronously
+        int flag = 0;
+        CUDA_TRY(cudaMemcpyAsync(&flag, ctx->d_err, sizeof(int), cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(cudaStreamSynchronize(s));
+        if (flag) return fail(FHE_EINVAL, "fhe_vec_modop: an element does not have a ModInverse using %llu", (unsigned long long)mod);
+    }
+    return FHE_OK;
+}
+
 extern "C" int fhe_vec_op_scalar(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, uint64_t scalar, size_t n,
                                  uint64_t q, int stream) {
     cudaStream_t s;
@@ -583,8 +622,16 @@ extern "C" int fhe_launch(fhe_ctx* ctx, int kernel_id, const void* desc, fhe_dpt
         case FHE_KERNEL_MOD_ADD: op = FHE_OP_ADD; break;
         case FHE_KERNEL_MOD_SUB: op = FHE_OP_SUB; break;
         case FHE_KERNEL_MOD_MULT: op = FHE_OP_MUL; break;
-        case FHE_KERNEL_MOD_OPS:
-            return fail(FHE_EUNSUPPORTED, "fhe_launch: mod-ops kernels are not connected (as in the reference, pim/PimData.h:171)");
+        case FHE_KERNEL_MOD_OPS: {
+            const mod_ops* o = (const mod_ops*)desc;
+            bool eq = o->kernel == SWITCHMODULUS || o->kernel == MODEQ || o->kernel == MODBYTWOEQ || o->kernel == MODEXPEQ ||
+                      o->kernel == MODINVERSEEQ || o->kernel == MULTIPLYANDROUNDEQ || o->kernel == DIVIDEANDROUNDEQ;
+            fhe_dptr src = heap_base + o->op.start, dst = eq ? src : heap_base + o->res.start;
+            int rc = fhe_vec_modop(ctx, (int)o->kernel, dst, src, o->op.size / sizeof(uint64_t), o->mod, o->p, o->q, FHE_STREAM_LEGACY);
+            if (rc) return rc;
+            CUDA_TRY(cudaStreamSynchronize(cudaStreamLegacy));
+            return FHE_OK;
+        }
         default: return fail(FHE_EINVAL, "fhe_launch: unknown kernel id %d", kernel_id);
     }
     const mod_add_sub_mult* m = (const mod_add_sub_mult*)desc;

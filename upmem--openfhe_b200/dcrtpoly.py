@@ -102,6 +102,10 @@ class Backend:
     def vec_op_scalar(self, op, dst, a, s, n, q, stream=0):
         N.check(N.lib.fhe_vec_op_scalar(self.h, op, dst, a, int(s), n, int(q), stream))
 
+    def vec_modop(self, kind, dst, src, n, mod, p=0, q=0, stream=0):
+        """kind: enum mod_kernel of pim/common.h (0 SWITCHMODULUS .. 12 DIVIDEANDROUNDEQ)."""
+        N.check(N.lib.fhe_vec_modop(self.h, kind, dst, src, n, int(mod), int(p), int(q), stream))
+
     def imad_probe(self, blocks, threads, iters):
         ms = ctypes.c_float()
         N.check(N.lib.fhe_imad_probe(self.h, blocks, threads, iters, ctypes.byref(ms)))
