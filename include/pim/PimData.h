@@ -139,15 +139,20 @@ public:
 
 private:
   struct Block {   /* one device allocation, freed when the last PimData sharing it dies */
-    PimManager *pim;
+    PimManager *pim = nullptr;
     std::vector<std::pair<size_t, uint32_t>> addrs;
+    Block() = default;
+    Block(const Block &) = delete;
+    Block &operator=(const Block &) = delete;
     ~Block() { if (pim && !addrs.empty()) pim->deallocate(addrs); }
   };
 
   void acquire() {
     metadata = pim->allocate(size);
     if (metadata.empty()) throw std::runtime_error("PimData: device heap exhausted");
-    block = std::make_shared<Block>(Block{pim, metadata});
+    block = std::make_shared<Block>();
+    block->pim = pim;
+    block->addrs = metadata;
   }
 
   uint32_t offset() const {
