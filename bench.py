@@ -13,8 +13,9 @@ per launch), several times the 126 MB L2, so no L2 flush is needed between itera
   cpu_baseline : the reference's own CPU path (oracle/_ref) on the host cores, rank 0, N=1 only
 
 `--impl reference` times only the CPU reference on the same config/metric.
-Multi-GPU: one process per GPU under torchrun; the batch dimension is sharded (weak scaling:
-256 polynomials per GPU), no data-path collective.
+Multi-GPU: one process per GPU under torchrun; the global batch (256 x N polynomials) is sharded
+by upmem--openfhe_b200/sharding.py (weak scaling: 256 polynomials per GPU), no data-path collective;
+NCCL carries the barrier, the max-over-ranks reduction and a checksum exchange of the results.
 """
 import argparse
 import importlib
@@ -157,13 +158,16 @@ def main():
     be = pkg.Backend(local, "streams=4,arena_mb=1024")
     q, psi = pkg.gen_params(NBITS, N_RING, TOWERS)
     ring = pkg.Ring(be, N_RING, q, psi)
+    sharding = importlib.import_module("upmem--openfhe_b200.sharding")
+    shard = sharding.plan(BATCH * world, TOWERS, world)[rank]      # this rank's block of the global batch
+    assert shard.batch == BATCH and shard.towers == TOWERS
     words = ring.words(BATCH)
     coeffs = words                                   # coefficient-ops per launch
     lib, ADD, MUL = pkg._native.lib, pkg.OP_ADD, pkg.OP_MUL
 
     da, db, dc, dd = (be.alloc(words * 8) for _ in range(4))
-    ring.fill_uniform(da, BATCH, 20260002 + rank * 7)
-    ring.fill_uniform(db, BATCH, 20261002 + rank * 7)
+    ring.fill_uniform(da, BATCH, 20260002 + shard.b0 * 7919)
+    ring.fill_uniform(db, BATCH, 20261002 + shard.b0 * 7919)
     be.sync()
 
     sampler = ClockSampler(local)
@@ -273,40 +277,49 @@ def main():
 
 
 def ntt_extra(pkg, be):
-    """Secondary figures: batched NTT+INTT at N=2^16 (BASELINE configs[2] shape, batch cut to fit a
-    short run) and the 64-bit multiply probe that calibrates the integer-pipe roofline."""
+    """Secondary figures (rank 0): batched forward / inverse NTT at BASELINE configs[2]'s shape
+    (N=2^16, 30 towers; batch cut to 64 so the run stays short, 1 GB in place > L2) against the
+    integer roofline.  Integer roofline = rate of lazy Shoup products (mulhi64 + 2 mullo64, the multiply
+    work of one butterfly) measured live by fhe_imad_probe; achieved = butterflies/s of the transform."""
     out = {}
     try:
-        n, towers, batch = 1 << 16, 30, 64
-        q, psi = pkg.gen_params(60, n, towers)
-        ring = pkg.Ring(be, n, q, psi)
-        words = ring.words(batch)
-        x = be.alloc(words * 8)
-        ring.fill_uniform(x, batch, 20260003)
-        for _ in range(3):
-            ring.ntt(x, batch, False); ring.ntt(x, batch, True)
-        be.sync()
-        reps = 10
-        be.timer_start(0)
-        for _ in range(reps):
-            ring.ntt(x, batch, False)
-        f_ms = be.timer_stop(0) / reps
-        be.timer_start(0)
-        for _ in range(reps):
-            ring.ntt(x, batch, True)
-        i_ms = be.timer_stop(0) / reps
-        peaks, _ = measured_peaks()
-        out["ntt_n65536_t30_b64"] = {
-            "fwd_ms": f_ms, "inv_ms": i_ms, "fwd_coeff_per_s": words / (f_ms * 1e-3), "inv_coeff_per_s": words / (i_ms * 1e-3),
-            "fwd_butterflies_per_s": words * 8 / (f_ms * 1e-3),
-            "fwd_hbm_gbs_2pass": 32 * words / (f_ms * 1e-3) / 1e9, "fwd_hbm_frac": 32 * words / (f_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
-        be.free(x)
-        ring.close()
         blocks, threads, iters = 148 * 8, 256, 4096
-        p_ms = be.imad_probe(blocks, threads, iters)
-        muls = blocks * threads * iters * 8
-        out["int_probe"] = {"mul64_hi_lo_pairs_per_s": muls / (p_ms * 1e-3), "ms": p_ms,
-                            "note": "each pair = __umul64hi + 64-bit mullo + add, 8 independent chains per thread"}
+        p_ms = min(be.imad_probe(blocks, threads, iters) for _ in range(3))
+        shoup_peak = blocks * threads * iters * 8 / (p_ms * 1e-3)
+        out["int_probe"] = {"shoup_products_per_s": shoup_peak, "ms": p_ms,
+                            "note": "8 independent chains of mulhi64 + 2 mullo64 per thread, 148x8 CTAs x 256 threads"}
+        peaks, _ = measured_peaks()
+        for logn, towers, batch in ((16, 30, 64), (14, 8, 256)):
+            n = 1 << logn
+            q, psi = pkg.gen_params(60, n, towers)
+            ring = pkg.Ring(be, n, q, psi)
+            words = ring.words(batch)
+            x = be.alloc(words * 8)
+            ring.fill_uniform(x, batch, 20260003)
+            for _ in range(3):
+                ring.ntt(x, batch, False); ring.ntt(x, batch, True)
+            be.sync()
+            reps = 10
+            be.timer_start(0)
+            for _ in range(reps):
+                ring.ntt(x, batch, False)
+            f_ms = be.timer_stop(0) / reps
+            be.timer_start(0)
+            for _ in range(reps):
+                ring.ntt(x, batch, True)
+            i_ms = be.timer_stop(0) / reps
+            bf = words * logn / 2                       # (N/2) log2 N butterflies per tower
+            out[f"ntt_n{n}_t{towers}_b{batch}"] = {
+                "fwd_ms": f_ms, "inv_ms": i_ms,
+                "fwd_coeff_per_s": words / (f_ms * 1e-3), "inv_coeff_per_s": words / (i_ms * 1e-3),
+                "roofline": {"bound": "integer pipe (fmaheavy)", "achieved": bf / (f_ms * 1e-3), "peak": shoup_peak,
+                             "unit": "butterflies/s vs Shoup products/s", "frac": bf / (f_ms * 1e-3) / shoup_peak,
+                             "frac_inverse": bf / (i_ms * 1e-3) / shoup_peak},
+                "hbm": {"algorithmic_bytes_per_coeff": 16, "moved_bytes_per_coeff": 32,
+                        "achieved_gbs_moved": 32 * words / (f_ms * 1e-3) / 1e9,
+                        "frac_of_measured_peak": 32 * words / (f_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}}
+            be.free(x)
+            ring.close()
     except Exception as ex:
         out["error"] = str(ex)[:300]
     return out

@@ -164,8 +164,9 @@ int fhe_dcrt_multi_op_host(fhe_ring* ring, const int* ops, int nops, uint64_t* c
 int fhe_ntt_host(fhe_ring* ring, uint64_t* x, size_t batch, int inverse);
 
 /* ---- diagnostics ---------------------------------------------------------------------------- */
-/* integer-pipe probe: launches blocks x threads, each thread doing iters x 8 (mulhi64 + mullo64);
- * returns the kernel time so the caller can derive 64-bit multiply throughput. */
+/* integer-pipe probe: launches blocks x threads, each thread doing iters x 8 lazy Shoup products
+ * (mulhi64 + 2 mullo64 = the multiply work of one NTT butterfly); returns the kernel time so the
+ * caller can derive the Shoup-product rate the NTT roofline is quoted against. */
 int fhe_imad_probe(fhe_ctx* ctx, int blocks, int threads, int iters, float* elapsed_ms);
 
 #ifdef __cplusplus

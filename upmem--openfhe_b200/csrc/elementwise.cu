@@ -238,14 +238,16 @@ cudaError_t launch_fill_uniform(const RingDev& r, uint64_t* dst, size_t batch, u
     return cudaGetLastError();
 }
 
-// ---- integer-pipe probe: 8 independent chains of 64x64->128 multiply-high + multiply-low ----
+// ---- integer-pipe probe: 8 independent chains of lazy Shoup products (mulhi64 + 2 mullo64), the
+// multiply work of one NTT butterfly.  Its rate is the integer roofline the NTT is reported against.
 __global__ void imad_probe_kernel(u64* out, int iters) {
-    u64 a[8], w = 0x9E3779B97F4A7C15ull + threadIdx.x;
+    u64 a[8], w = 0x9E3779B97F4A7C15ull + threadIdx.x, wp = w ^ 0x5555555555555555ull;
+    const u64 nq = 0ull - (0x0FFFFFFFFFFC0001ull);
 #pragma unroll
     for (int k = 0; k < 8; k++) a[k] = w * (k + 3) + blockIdx.x;
     for (int it = 0; it < iters; it++) {
 #pragma unroll
-        for (int k = 0; k < 8; k++) a[k] = __umul64hi(a[k], w) + a[k] * w;
+        for (int k = 0; k < 8; k++) a[k] = shoup_lazy(a[k], w, wp, nq);
     }
     u64 s = 0;
 #pragma unroll
