@@ -236,7 +236,20 @@ def main():
         ring.multi_op_host([ADD, MUL], [hc, hd], ha, hb, BATCH)
     be.sync()
     e2e_s = max_over_ranks(dist, local, time.perf_counter() - t0)
+    # PCIe ceiling for this access pattern: both directions busy at once, pinned memory, same sizes
+    N_ = pkg._native
+    be.sync()
+    t0 = time.perf_counter()
+    N_.check(N_.lib.fhe_h2d(be.h, da, pa, words * 8, 0))
+    N_.check(N_.lib.fhe_d2h(be.h, pc, dc, words * 8, 1))
+    be.sync()
+    pcie_both = words * 8 / (time.perf_counter() - t0) / 1e9
+    ring.fill_uniform(da, BATCH, 20260002 + shard.b0 * 7919)
+    be.sync()
     e2e = {"value": world * 2 * coeffs * e2e_steps / e2e_s, "unit": UNIT,
+           "pcie": {"achieved_gbs_each_way": 2 * words * 8 / (e2e_s / e2e_steps) / 1e9,
+                    "ceiling_gbs_each_way_bidirectional": pcie_both,
+                    "note": "the host-operand path is PCIe-bound: 24 B cross the bus per coefficient-op"},
            "h2d_bytes_per_step": 2 * words * 8, "d2h_bytes_per_step": 2 * words * 8, "steps": e2e_steps,
            "ms_per_step": 1e3 * e2e_s / e2e_steps,
            "api": "fhe_dcrt_multi_op_host(ADD, MUL): pinned host operands, chunked H2D/kernel/D2H over 4 streams"}

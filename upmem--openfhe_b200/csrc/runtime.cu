@@ -139,6 +139,7 @@ struct fhe_ctx {
     std::mutex mu;
     std::map<int, Timer> timers;
     std::vector<void*> pinned;
+    size_t chunk_bytes = 32ull << 20;   // host pipelines: bytes per operand per chunk (opts: chunk_mb)
     int* d_err = nullptr;          // device flag written by kernels that can meet invalid elements
 };
 
@@ -198,6 +199,7 @@ extern "C" int fhe_init(int device, const char* opts, fhe_ctx** out) {
     ctx->device = device;
     long ns = std::max(1l, std::min(64l, opt_value(opts, "streams", 4)));
     ctx->arena.slab_bytes = (size_t)std::max(1l, opt_value(opts, "arena_mb", 256)) << 20;
+    ctx->chunk_bytes = (size_t)std::max(1l, std::min(1024l, opt_value(opts, "chunk_mb", 32))) << 20;
     for (long i = 0; i < ns; i++) {
         cudaStream_t s;
         e = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
@@ -662,7 +664,7 @@ struct HostPipe {
     HostPipe(fhe_ring* ring, bool two_operands) : r(ring) {
         item_words = (size_t)r->dev.T * r->dev.N;
         size_t item_bytes = item_words * 8;
-        chunk_items = std::max<size_t>(1, (32ull << 20) / item_bytes);
+        chunk_items = std::max<size_t>(1, r->ctx->chunk_bytes / item_bytes);
         nslots = std::min<size_t>(r->ctx->streams.size(), 4);
         (void)two_operands;
     }
