@@ -107,7 +107,8 @@ int fhe_gen_params(uint32_t nbits, uint32_t N, uint32_t towers, uint64_t* q, uin
 uint64_t fhe_root_of_unity(uint64_t m, uint64_t q);              /* 0 if m does not divide q-1 */
 
 /* ---- ring --------------------------------------------------------------------------------- */
-/* N power of two, 1 <= N <= 65536; 4 <= q_i < 2^61; psi_i a primitive 2N-th root mod q_i
+/* N power of two, 1 <= N <= 65536; 4 <= q_i < 2^61 (< 2^60 when psi is given: the reference's
+ * MAX_MODULUS_SIZE, basicint.h:44-45); psi_i a primitive 2N-th root mod q_i
  * (psi may be NULL when only fhe_dcrt_op is needed).  Builds the Barrett constants and, per
  * tower, the four tables PreCompute builds, and keeps them in HBM. */
 int fhe_ring_create(fhe_ctx* ctx, uint32_t N, uint32_t towers, const uint64_t* q,

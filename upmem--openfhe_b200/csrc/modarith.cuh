@@ -70,19 +70,43 @@ __device__ __forceinline__ u64 shoup(u64 x, u64 w, u64 wp, u64 q) {
     return csub(shoup_lazy(x, w, wp, 0ull - q), q);
 }
 
-// Harvey butterflies.  q2 = 2q, nq = -q mod 2^64.
-// Forward (Cooley-Tukey): X, Y in [0,4q) -> X, Y in [0,4q).
-__device__ __forceinline__ void fwd_bf(u64& X, u64& Y, u64 w, u64 wp, u64 q2, u64 nq) {
-    u64 x = csub(X, q2);
-    u64 t = shoup_lazy(Y, w, wp, nq);
-    X = x + t;
-    Y = x - t + q2;
+// ---- lazy butterflies with compile-time range tracking ---------------------------------------
+// Every modulus on the NTT path is below 2^60 (the reference's MAX_MODULUS_SIZE, basicint.h:44-45), so a
+// 64-bit word holds values up to 16q.  Values are kept in [0, B*q) with B known at compile time and
+// are only pulled back (conditional subtractions of 8q, 4q, 2q, q) where B would pass 16; the last
+// store of a transform reduces to [0,q), so results equal the reference's fully reduced ones.
+struct QMul { u64 q1, q2, q4, q8; };            // q, 2q, 4q, 8q
+__device__ __forceinline__ QMul make_qmul(u64 q) { return QMul{q, 2 * q, 4 * q, 8 * q}; }
+
+template <int M>
+__device__ __forceinline__ u64 qm(const QMul& Q) {
+    static_assert(M == 1 || M == 2 || M == 4 || M == 8, "multiple of q not kept in registers");
+    return M == 1 ? Q.q1 : M == 2 ? Q.q2 : M == 4 ? Q.q4 : Q.q8;
 }
-// Inverse (Gentleman-Sande): X, Y in [0,2q) -> X, Y in [0,2q).
-__device__ __forceinline__ void inv_bf(u64& X, u64& Y, u64 w, u64 wp, u64 q2, u64 nq) {
-    u64 s = X + Y;
-    u64 d = X - Y + q2;
-    X = csub(s, q2);
+
+// [0, FROM*q) -> [0, TO*q), FROM <= 16, by conditional subtractions of the power-of-two multiples.
+template <int FROM, int TO>
+__device__ __forceinline__ u64 reduce_range(u64 x, const QMul& Q) {
+    if constexpr (FROM <= TO) {
+        return x;
+    } else {
+        constexpr int M = FROM > 8 ? 8 : FROM > 4 ? 4 : FROM > 2 ? 2 : 1;   // largest kept multiple below FROM
+        constexpr int NEXT = (FROM - M) > M ? (FROM - M) : M;
+        return reduce_range<NEXT, TO>(csub(x, qm<M>(Q)), Q);
+    }
+}
+
+// Forward (Cooley-Tukey): X in [0,Bq), Y anything below 2^64 -> both in [0,(B+2)q).  No reduction of X.
+__device__ __forceinline__ void fwd_bf(u64& X, u64& Y, u64 w, u64 wp, u64 q2, u64 nq) {
+    u64 t = shoup_lazy(Y, w, wp, nq);            // [0,2q)
+    Y = X - t + q2;
+    X = X + t;
+}
+// Inverse (Gentleman-Sande): X in [0,BXq), Y in [0,BYq) -> X in [0,(BX+BY)q), Y in [0,2q).
+// byq = BY*q keeps the difference non-negative.
+__device__ __forceinline__ void inv_bf(u64& X, u64& Y, u64 w, u64 wp, u64 byq, u64 nq) {
+    u64 d = X - Y + byq;
+    X = X + Y;
     Y = shoup_lazy(d, w, wp, nq);
 }
 

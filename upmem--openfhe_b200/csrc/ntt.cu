@@ -22,63 +22,150 @@
 #include "modarith.cuh"
 #include "kernels.h"
 
+#include <type_traits>
+
 namespace fhe {
 
 __device__ __forceinline__ ulonglong2 ldtw(const ulonglong2* __restrict__ p) { return __ldg(p); }
 
-// One butterfly stage J (of S) on E = 2^S register-resident coefficients.  The coefficients are
-// the sub-NTT whose twiddle prefix is P: stage J uses table[(P << J) + (e >> (S-J))].
-template <int S, int J, bool INV>
-__device__ __forceinline__ void reg_stage(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw, u32 P,
+template <int I, int N, class F>
+__device__ __forceinline__ void static_for(F&& f) {
+    if constexpr (I < N) {
+        f(std::integral_constant<int, I>{});
+        static_for<I + 1, N>(f);
+    }
+}
+
+constexpr int MAXB = 16;
+constexpr int INV_NORM = 4;  // uniform bound the inverse restores between register steps and between the two passes     // values stay below MAXB*q < 2^64 (q < 2^60)
+
+// ---- forward: E = bound (in units of q) of every coefficient entering a step of S stages.
+// A stage adds 2 to the bound of both outputs whatever the bound of the multiplied input, so only the
+// elements that are NOT multiplied in the first stage have to be pulled below 16 - 2S on entry.
+template <int S, int E>
+struct FwdStep {
+    static constexpr int LIM = MAXB - 2 * S;
+    static constexpr int XB  = E > LIM ? 8 : E;          // after one conditional subtraction of 8q
+    static constexpr int OUT = XB + 2 * S;
+    static_assert(E <= MAXB && OUT <= MAXB, "forward step overflows the 16q headroom");
+};
+
+// One butterfly stage J (of S) on 2^S register-resident coefficients.  The coefficients are the
+// sub-NTT whose twiddle prefix is P: stage J uses table[(P << J) + (e >> (S-J))].
+template <int S, int J>
+__device__ __forceinline__ void fwd_stage(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw, u32 P,
                                           u64 q2, u64 nq) {
     constexpr int half = 1 << (S - 1 - J);
 #pragma unroll
     for (int g = 0; g < (1 << J); g++) {
         ulonglong2 w = ldtw(tw + ((P << J) + g));
 #pragma unroll
-        for (int i = 0; i < half; i++) {
-            if (!INV) fwd_bf(x[g * 2 * half + i], x[g * 2 * half + i + half], w.x, w.y, q2, nq);
-            else      inv_bf(x[g * 2 * half + i], x[g * 2 * half + i + half], w.x, w.y, q2, nq);
-        }
+        for (int i = 0; i < half; i++) fwd_bf(x[g * 2 * half + i], x[g * 2 * half + i + half], w.x, w.y, q2, nq);
     }
 }
 
-// Stages [J0, J1) in transform order: ascending for the forward CT, descending for the inverse GS.
-template <int S, int J0, int J1, bool INV>
-__device__ __forceinline__ void reg_stages(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw, u32 P,
-                                           u64 q2, u64 nq) {
-    if constexpr (J0 < J1) {
-        if constexpr (!INV) {
-            reg_stage<S, J0, false>(x, tw, P, q2, nq);
-            reg_stages<S, J0 + 1, J1, false>(x, tw, P, q2, nq);
-        } else {
-            reg_stage<S, J1 - 1, true>(x, tw, P, q2, nq);
-            reg_stages<S, J0, J1 - 1, true>(x, tw, P, q2, nq);
+template <int S, int E>
+__device__ __forceinline__ void fwd_step(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw, u32 P,
+                                         const QMul& Q, u64 nq) {
+    if constexpr (S > 0) {
+        if constexpr (E > FwdStep<S, E>::LIM) {
+#pragma unroll
+            for (int e = 0; e < (1 << (S - 1)); e++) x[e] = csub(x[e], Q.q8);
         }
+        static_for<0, S>([&](auto j) { fwd_stage<S, decltype(j)::value>(x, tw, P, Q.q2, nq); });
     }
 }
 
-template <int S, bool INV>
-__device__ __forceinline__ void reg_step(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw, u32 P,
-                                         u64 q2, u64 nq) {
-    reg_stages<S, 0, S, INV>(x, tw, P, q2, nq);
+// ---- inverse: the sum output doubles the bound, the multiplied output comes back in [0,2q), so the
+// bounds differ per register.  The schedule of conditional subtractions is simulated at compile time.
+template <int S>
+struct InvPlan {
+    int cur[S + 1][1 << S];   // bound of register e before stage k (k-th executed: J = S-1-k), before `tgt`
+    int tgt[S + 1][1 << S];   // bound register e is reduced to before stage k (== cur: nothing to do)
+    int out;                  // uniform bound after the closing normalisation (row S of cur -> tgt)
+};
+
+template <int S>
+constexpr InvPlan<S> make_inv_plan(int E, int NORM) {
+    InvPlan<S> p{};
+    int b[1 << S] = {};
+    for (int e = 0; e < (1 << S); e++) b[e] = E;
+    for (int k = 0; k < S; k++) {
+        int half = 1 << k;                                  // executed order: J = S-1 first (half 1)
+        for (int e = 0; e < (1 << S); e++) { p.cur[k][e] = b[e]; p.tgt[k][e] = b[e]; }
+        for (int e = 0; e < (1 << S); e++) {
+            if (e & half) continue;
+            int bx = b[e], by = b[e + half];
+            while (bx + by > MAXB || by > 8) {              // by*q must be one of q,2q,4q,8q
+                if (bx >= by) bx = bx > 8 ? 8 : bx / 2; else by = by > 8 ? 8 : by / 2;
+            }
+            p.tgt[k][e] = bx; p.tgt[k][e + half] = by;
+            b[e] = bx + by; b[e + half] = 2;
+        }
+    }
+    for (int e = 0; e < (1 << S); e++) {
+        p.cur[S][e] = b[e];
+        p.tgt[S][e] = b[e] > NORM ? NORM : b[e];
+    }
+    p.out = NORM;
+    return p;
+}
+
+template <int S, int E, int NORM>
+struct InvStep {
+    static constexpr InvPlan<S> P = make_inv_plan<S>(E, NORM);
+};
+
+// executed stage K (J = S-1-K) of an inverse step
+template <int S, int E, int NORM, int K>
+__device__ __forceinline__ void inv_stage(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw, u32 P,
+                                          const QMul& Q, u64 nq) {
+    constexpr int J = S - 1 - K, half = 1 << K;
+    using PL = InvStep<S, E, NORM>;
+    static_for<0, (1 << J)>([&](auto gi) {
+        constexpr int g = decltype(gi)::value;
+        ulonglong2 w = ldtw(tw + ((P << J) + g));
+        static_for<0, half>([&](auto ii) {
+            constexpr int a = g * 2 * half + decltype(ii)::value, b = a + half;
+            constexpr int BY = PL::P.tgt[K][b];
+            x[a] = reduce_range<PL::P.cur[K][a], PL::P.tgt[K][a]>(x[a], Q);
+            x[b] = reduce_range<PL::P.cur[K][b], BY>(x[b], Q);
+            inv_bf(x[a], x[b], w.x, w.y, qm<(BY < 1 ? 1 : BY)>(Q), nq);
+        });
+    });
+}
+
+// all S stages, then normalisation of every register to [0, NORM*q)
+template <int S, int E, int NORM>
+__device__ __forceinline__ void inv_step(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw, u32 P,
+                                         const QMul& Q, u64 nq) {
+    using PL = InvStep<S, E, NORM>;
+    static_for<0, S>([&](auto k) { inv_stage<S, E, NORM, decltype(k)::value>(x, tw, P, Q, nq); });
+    static_for<0, (1 << S)>([&](auto ei) {
+        constexpr int e = decltype(ei)::value;
+        x[e] = reduce_range<PL::P.cur[S][e], PL::P.tgt[S][e]>(x[e], Q);
+    });
 }
 
 // Inverse step that contains the very last stage of the whole transform (global stage m = 1):
 // folds N^-1 into it like transformnat-impl.h:497-524 folds it into the first one, and reduces
 // both outputs to [0,q).  sc = {N^-1, companion}, w1 = {WI[1]*N^-1 mod q, companion}.
-template <int S>
-__device__ __forceinline__ void reg_step_inv_last(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw,
-                                                  ulonglong2 sc, ulonglong2 w1, u64 q, u64 q2, u64 nq) {
-    reg_stages<S, 1, S, true>(x, tw, 1u, q2, nq);
-    constexpr int half = 1 << (S - 1);
-#pragma unroll
-    for (int i = 0; i < half; i++) {
-        u64 s = x[i] + x[i + half];
-        u64 d = x[i] - x[i + half] + q2;
-        x[i]        = csub(shoup_lazy(s, sc.x, sc.y, nq), q);
-        x[i + half] = csub(shoup_lazy(d, w1.x, w1.y, nq), q);
-    }
+template <int S, int E>
+__device__ __forceinline__ void inv_step_last(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw,
+                                              ulonglong2 sc, ulonglong2 w1, const QMul& Q, u64 nq) {
+    using PL = InvStep<S, E, MAXB>;
+    static_for<0, S - 1>([&](auto k) { inv_stage<S, E, MAXB, decltype(k)::value>(x, tw, 1u, Q, nq); });
+    constexpr int K = S - 1, half = 1 << K;
+    static_for<0, half>([&](auto ii) {
+        constexpr int a = decltype(ii)::value, b = a + half;
+        constexpr int BY = PL::P.tgt[K][b];
+        x[a] = reduce_range<PL::P.cur[K][a], PL::P.tgt[K][a]>(x[a], Q);
+        x[b] = reduce_range<PL::P.cur[K][b], BY>(x[b], Q);
+        u64 s = x[a] + x[b];
+        u64 d = x[a] - x[b] + qm<(BY < 1 ? 1 : BY)>(Q);
+        x[a] = csub(shoup_lazy(s, sc.x, sc.y, nq), Q.q1);
+        x[b] = csub(shoup_lazy(d, w1.x, w1.y, nq), Q.q1);
+    });
 }
 
 // ------------------------------------------------------------------------------------------
@@ -110,7 +197,8 @@ ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
     const u32 unit  = blockIdx.x / tilesPerUnit;
     const u32 cg    = blockIdx.x % tilesPerUnit;
     const u32 tower = unit % T;
-    const u64 q = mods[tower].q, q2 = 2 * q, nq = 0ull - q;
+    const u64 q = mods[tower].q, nq = 0ull - q;
+    const QMul Q = make_qmul(q);
     const ulonglong2* tw = twAll + ((size_t)tower << logN);
     u64* base = data + ((size_t)unit << logN) + cg * C;
     const u32 tid = threadIdx.x;
@@ -124,7 +212,7 @@ ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
             u64 x[1 << A];
 #pragma unroll
             for (int e = 0; e < (1 << A); e++) x[e] = base[((size_t)((e << B) + ulow) << 8) + c];
-            reg_step<A, false>(x, tw, 1u, q2, nq);
+            fwd_step<A, 1>(x, tw, 1u, Q, nq);
             if (B == 0) {
 #pragma unroll
                 for (int e = 0; e < (1 << A); e++) base[((size_t)((e << B) + ulow) << 8) + c] = x[e];
@@ -142,7 +230,7 @@ ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
                 u64 x[1 << B];
 #pragma unroll
                 for (int e = 0; e < (1 << B); e++) x[e] = sm[((uhi << B) + e) * C + c];
-                reg_step<B, false>(x, tw, (1u << A) + uhi, q2, nq);
+                fwd_step<B, FwdStep<A, 1>::OUT>(x, tw, (1u << A) + uhi, Q, nq);
 #pragma unroll
                 for (int e = 0; e < (1 << B); e++) base[((size_t)((uhi << B) + e) << 8) + c] = x[e];
             }
@@ -157,7 +245,7 @@ ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
                 u64 x[1 << B];
 #pragma unroll
                 for (int e = 0; e < (1 << B); e++) x[e] = base[((size_t)((uhi << B) + e) << 8) + c];
-                reg_step<B, true>(x, tw, (1u << A) + uhi, q2, nq);
+                inv_step<B, INV_NORM, INV_NORM>(x, tw, (1u << A) + uhi, Q, nq);
 #pragma unroll
                 for (int e = 0; e < (1 << B); e++) sm[((uhi << B) + e) * C + c] = x[e];
             }
@@ -175,7 +263,7 @@ ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
 #pragma unroll
                 for (int e = 0; e < (1 << A); e++) x[e] = base[((size_t)((e << B) + ulow) << 8) + c];
             }
-            reg_step_inv_last<A>(x, tw, sc, w1, q, q2, nq);
+            inv_step_last<A, INV_NORM>(x, tw, sc, w1, Q, nq);
 #pragma unroll
             for (int e = 0; e < (1 << A); e++) base[((size_t)((e << B) + ulow) << 8) + c] = x[e];
         }
@@ -204,7 +292,8 @@ ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
     const u32 hg = bid % hgroups; bid /= hgroups;
     const u32 bg = bid % bgroups;
     const u32 tower = bid / bgroups;
-    const u64 q = mods[tower].q, q2 = 2 * q, nq = 0ull - q;
+    const u64 q = mods[tower].q, nq = 0ull - q;
+    const QMul Q = make_qmul(q);
     const ulonglong2* tw = twAll + ((size_t)tower << logN);
     const u32 tid = threadIdx.x;
 
@@ -222,7 +311,7 @@ ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
             u64 x[16];
 #pragma unroll
             for (int e = 0; e < 16; e++) x[e] = ok ? p[e * 16 + ulow] : 0ull;
-            reg_step<4, false>(x, tw, N1 + h, q2, nq);
+            fwd_step<4, MAXB>(x, tw, N1 + h, Q, nq);          // entry: whatever the strided pass left, < 16q
 #pragma unroll
             for (int e = 0; e < 16; e++) sm[(e * 16 + ulow) * CT_PITCH + c] = x[e];
         }
@@ -233,9 +322,9 @@ ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
             u64 x[16];
 #pragma unroll
             for (int e = 0; e < 16; e++) x[e] = sm[(uhi * 16 + e) * CT_PITCH + c];
-            reg_step<4, false>(x, tw, ((N1 + h) << 4) + uhi, q2, nq);
+            fwd_step<4, FwdStep<4, MAXB>::OUT>(x, tw, ((N1 + h) << 4) + uhi, Q, nq);
 #pragma unroll
-            for (int e = 0; e < 16; e++) sm[(uhi * 16 + e) * CT_PITCH + c] = csub(csub(x[e], q2), q);
+            for (int e = 0; e < 16; e++) sm[(uhi * 16 + e) * CT_PITCH + c] = reduce_range<FwdStep<4, FwdStep<4, MAXB>::OUT>::OUT, 1>(x[e], Q);
         }
         __syncthreads();
 #pragma unroll
@@ -258,7 +347,7 @@ ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
             u64 x[16];
 #pragma unroll
             for (int e = 0; e < 16; e++) x[e] = sm[(uhi * 16 + e) * CT_PITCH + c];
-            reg_step<4, true>(x, tw, ((N1 + h) << 4) + uhi, q2, nq);
+            inv_step<4, 1, INV_NORM>(x, tw, ((N1 + h) << 4) + uhi, Q, nq);
 #pragma unroll
             for (int e = 0; e < 16; e++) sm[(uhi * 16 + e) * CT_PITCH + c] = x[e];
         }
@@ -269,10 +358,10 @@ ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
             u64 x[16];
 #pragma unroll
             for (int e = 0; e < 16; e++) x[e] = sm[(e * 16 + ulow) * CT_PITCH + c];
-            reg_step<4, true>(x, tw, N1 + h, q2, nq);
+            inv_step<4, INV_NORM, INV_NORM>(x, tw, N1 + h, Q, nq);
             if (ok) {
 #pragma unroll
-                for (int e = 0; e < 16; e++) p[e * 16 + ulow] = x[e];   // lazily reduced, [0,2q)
+                for (int e = 0; e < 16; e++) p[e * 16 + ulow] = x[e];   // lazily reduced, [0, INV_NORM*q)
             }
         }
     }

@@ -425,6 +425,11 @@ extern "C" int fhe_ring_create(fhe_ctx* ctx, uint32_t N, uint32_t T, const uint6
             return fail(FHE_EUNSUPPORTED, "fhe_ring_create: mixing trivial (0/1) and real roots of unity is not supported");
         } else {
             for (uint32_t t = 0; t < T; t++) {
+                if (q[t] >= (1ull << 60)) {      // lazy butterflies keep values below 16q in a 64-bit word
+                    fhe_ring_destroy(r);
+                    return fail(FHE_EUNSUPPORTED, "fhe_ring_create: NTT needs moduli below 2^60 (the reference's MAX_MODULUS_SIZE); modulus %u = %llu",
+                                t, (unsigned long long)q[t]);
+                }
                 bool ok = N == 1 ? (psi[t] % q[t] == q[t] - 1) : (host::powmod(psi[t], N, q[t]) == q[t] - 1);
                 if (!ok || psi[t] >= q[t]) {
                     fhe_ring_destroy(r);
