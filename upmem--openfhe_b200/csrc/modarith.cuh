@@ -62,7 +62,21 @@ __device__ __forceinline__ u64 csub(u64 x, u64 m) {
 // ride on the multiply-add chain.
 __device__ __forceinline__ u64 shoup_lazy(u64 x, u64 w, u64 wp, u64 nq) {
     u64 qh = __umul64hi(x, wp);
-    return x * w + qh * nq;
+    // low 64 bits of x*w + qh*nq with every 32x32 partial product accumulated by the multiplier itself
+    // (2 IMAD.WIDE + 4 IMAD chained through the high word, no separate adds)
+    u32 x0 = (u32)x, x1 = (u32)(x >> 32), w0 = (u32)w, w1 = (u32)(w >> 32);
+    u32 h0 = (u32)qh, h1 = (u32)(qh >> 32), n0 = (u32)nq, n1 = (u32)(nq >> 32);
+    u64 acc;
+    u32 lo, hi;
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(acc) : "r"(x0), "r"(w0));
+    asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(h0), "r"(n0));
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(acc));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(x0), "r"(w1));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(x1), "r"(w0));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(h0), "r"(n1));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(h1), "r"(n0));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(acc) : "r"(lo), "r"(hi));
+    return acc;
 }
 
 // Fully reduced Shoup product (what ModMulFastConstEq returns).

@@ -22,6 +22,7 @@
 #include "modarith.cuh"
 #include "kernels.h"
 
+#include <cstdlib>
 #include <type_traits>
 
 namespace fhe {
@@ -36,6 +37,7 @@ __device__ __forceinline__ void static_for(F&& f) {
     }
 }
 
+constexpr int NTT_TILE_LOG_DEFAULT[2] = {11, 10};   // {strided, contig}: measured best on B200 (profiles/)
 constexpr int MAXB = 16;
 constexpr int INV_NORM = 4;  // uniform bound the inverse restores between register steps and between the two passes     // values stay below MAXB*q < 2^64 (q < 2^60)
 
@@ -173,24 +175,31 @@ __device__ __forceinline__ void inv_step_last(u64 (&x)[1 << S], const ulonglong2
 // Forward: stages 0..RL-1 of the transform (twiddle prefix 1).  Inverse: the same stages in
 // reverse order, run AFTER the contig pass, ending with the N^-1 stage.
 // ------------------------------------------------------------------------------------------
-template <int RL>
+// TL = log2(coefficients per tile): 12 -> 256 threads, 11 -> 128, 10 -> 64, 9 -> one warp.  Smaller tiles mean more,
+// smaller CTAs per SM whose load / compute / store phases interleave.
+template <int RL, int TL>
 struct StridedCfg {
     static constexpr int A = RL < 4 ? RL : 4;          // stages done on the top bits of the row index
     static constexpr int B = RL - A;                   // stages done on the low bits
     static constexpr int R = 1 << RL;
-    static constexpr int C = (4096 / R) < 256 ? (4096 / R) : 256;
+    static constexpr int C = ((1 << TL) / R) < 256 ? ((1 << TL) / R) : 256;
     static constexpr int THREADS = R * C / 16;
     static constexpr int GA = 16 >> A;                 // register groups per thread in step A
     static constexpr int GB = 16 >> B;
-    static constexpr int SMEM = (B > 0) ? R * C * 8 : 0;
+    // exchange buffer [row][C]; C < 16: one extra row of padding per 2^B rows keeps the c-major reads
+    // of two neighbouring sub-NTTs in different banks
+    static constexpr int PAD = (B > 0 && C < 16) ? C : 0;
+    static constexpr int SMEM = (B > 0) ? (R * C + (R >> B) * PAD) * 8 : 0;
+    static_assert(THREADS >= 32 || RL < 4, "tile too small");
 };
 
-template <int RL, bool INV>
-__global__ void __launch_bounds__(StridedCfg<RL>::THREADS)
+template <int RL, int TL, bool INV>
+__global__ void __launch_bounds__(StridedCfg<RL, TL>::THREADS)
 ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
                    const TowerMod* __restrict__ mods, const ulonglong2* __restrict__ invc,
                    u32 T, u32 logN) {
-    using K = StridedCfg<RL>;
+    using K = StridedCfg<RL, TL>;
+    auto sidx = [](u32 row, u32 c) -> u32 { return row * K::C + c + (row >> K::B) * K::PAD; };
     extern __shared__ __align__(16) u64 sm[];
     constexpr int A = K::A, B = K::B, C = K::C;
     const u32 tilesPerUnit = 256 / C;
@@ -218,7 +227,7 @@ ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
                 for (int e = 0; e < (1 << A); e++) base[((size_t)((e << B) + ulow) << 8) + c] = x[e];
             } else {
 #pragma unroll
-                for (int e = 0; e < (1 << A); e++) sm[((e << B) + ulow) * C + c] = x[e];
+                for (int e = 0; e < (1 << A); e++) sm[sidx((e << B) + ulow, c)] = x[e];
             }
         }
         if (B > 0) {
@@ -229,7 +238,7 @@ ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
                 u32 c = item % C, uhi = item / C;
                 u64 x[1 << B];
 #pragma unroll
-                for (int e = 0; e < (1 << B); e++) x[e] = sm[((uhi << B) + e) * C + c];
+                for (int e = 0; e < (1 << B); e++) x[e] = sm[sidx((uhi << B) + e, c)];
                 fwd_step<B, FwdStep<A, 1>::OUT>(x, tw, (1u << A) + uhi, Q, nq);
 #pragma unroll
                 for (int e = 0; e < (1 << B); e++) base[((size_t)((uhi << B) + e) << 8) + c] = x[e];
@@ -247,7 +256,7 @@ ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
                 for (int e = 0; e < (1 << B); e++) x[e] = base[((size_t)((uhi << B) + e) << 8) + c];
                 inv_step<B, INV_NORM, INV_NORM>(x, tw, (1u << A) + uhi, Q, nq);
 #pragma unroll
-                for (int e = 0; e < (1 << B); e++) sm[((uhi << B) + e) * C + c] = x[e];
+                for (int e = 0; e < (1 << B); e++) sm[sidx((uhi << B) + e, c)] = x[e];
             }
             __syncthreads();
         }
@@ -258,7 +267,7 @@ ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
             u64 x[1 << A];
             if (B > 0) {
 #pragma unroll
-                for (int e = 0; e < (1 << A); e++) x[e] = sm[((e << B) + ulow) * C + c];
+                for (int e = 0; e < (1 << A); e++) x[e] = sm[sidx((e << B) + ulow, c)];
             } else {
 #pragma unroll
                 for (int e = 0; e < (1 << A); e++) x[e] = base[((size_t)((e << B) + ulow) << 8) + c];
@@ -272,20 +281,30 @@ ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
 
 // ------------------------------------------------------------------------------------------
 // Contig pass: 256-point sub-NTTs over contiguous blocks (transform stages L-8..L-1).
-// Tile = 16 sub-NTTs: CB batch items x CH consecutive blocks (CB*CH = 16), 256 threads.
-// Shared layout [u][c] with row pitch 17 so both the u-major and the c-major accesses are
-// bank-conflict free.
+// Tile = NC = 2^LB sub-NTTs (16, 8 or 4): CB batch items x CH consecutive blocks (CB*CH = NC),
+// 16*NC threads.  Shared layout [u][c] with the column XOR-swizzled by bits of u (and, for NC < 16, NC
+// words of padding per 16 rows): the u-major, c-major and transposed accesses are all conflict-free.
 // ------------------------------------------------------------------------------------------
-constexpr int CT_PITCH = 17;
-constexpr int CT_SMEM  = 256 * CT_PITCH * 8;
+template <int LB>
+struct ContigCfg {
+    static constexpr int NC = 1 << LB, THREADS = 16 * NC;
+    static constexpr int SMEM = (256 * NC + (LB < 4 ? 16 * NC : 0)) * 8;
+    __device__ static __forceinline__ u32 idx(u32 u, u32 c) {
+        u32 a = u * NC + (c ^ ((u >> (4 - LB)) & (NC - 1)));
+        if (LB < 4) a += (u >> 4) * NC;
+        return a;
+    }
+};
 
-template <bool INV>
-__global__ void __launch_bounds__(256)
+template <int LB, bool INV>
+__global__ void __launch_bounds__(ContigCfg<LB>::THREADS)
 ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
                   const TowerMod* __restrict__ mods, u32 T, u32 logN, u32 batch, u32 logCB) {
+    using K = ContigCfg<LB>;
+    constexpr u32 NC = K::NC, TH = K::THREADS;
     extern __shared__ __align__(16) u64 sm[];
     const u32 N1 = 1u << (logN - 8);
-    const u32 CB = 1u << logCB, CH = 16u >> logCB;
+    const u32 CB = 1u << logCB, CH = NC >> logCB;
     const u32 hgroups = N1 / CH;                      // N1 >= CH is guaranteed by the launcher
     const u32 bgroups = (batch + CB - 1) / CB;
     u32 bid = blockIdx.x;
@@ -313,43 +332,48 @@ ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
             for (int e = 0; e < 16; e++) x[e] = ok ? p[e * 16 + ulow] : 0ull;
             fwd_step<4, MAXB>(x, tw, N1 + h, Q, nq);          // entry: whatever the strided pass left, < 16q
 #pragma unroll
-            for (int e = 0; e < 16; e++) sm[(e * 16 + ulow) * CT_PITCH + c] = x[e];
+            for (int e = 0; e < 16; e++) sm[K::idx(e * 16 + ulow, c)] = x[e];
         }
         __syncthreads();
         {   // step B: lanes run along c, registers hold the low 4 bits of u
-            u32 c = tid & 15, uhi = tid >> 4, h; bool ok;
+            u32 c = tid & (NC - 1), uhi = tid >> LB, h; bool ok;
             (void)blk_ptr(c, ok, h);
             u64 x[16];
 #pragma unroll
-            for (int e = 0; e < 16; e++) x[e] = sm[(uhi * 16 + e) * CT_PITCH + c];
+            for (int e = 0; e < 16; e++) x[e] = sm[K::idx(uhi * 16 + e, c)];
             fwd_step<4, FwdStep<4, MAXB>::OUT>(x, tw, ((N1 + h) << 4) + uhi, Q, nq);
 #pragma unroll
-            for (int e = 0; e < 16; e++) sm[(uhi * 16 + e) * CT_PITCH + c] = reduce_range<FwdStep<4, FwdStep<4, MAXB>::OUT>::OUT, 1>(x[e], Q);
+            for (int e = 0; e < 16; e++)
+                sm[K::idx(uhi * 16 + e, c)] = reduce_range<FwdStep<4, FwdStep<4, MAXB>::OUT>::OUT, 1>(x[e], Q);
         }
         __syncthreads();
 #pragma unroll
-        for (int k = 0; k < 16; k++) {               // coalesced write-back, fully reduced
+        for (u32 k = 0; k < NC; k++) {               // coalesced write-back, fully reduced
             u32 h; bool ok;
             u64* p = blk_ptr(k, ok, h);
-            if (ok) p[tid] = sm[tid * CT_PITCH + k];
+            if (ok) {
+#pragma unroll
+                for (u32 u = tid; u < 256; u += TH) p[u] = sm[K::idx(u, k)];
+            }
         }
     } else {
 #pragma unroll
-        for (int k = 0; k < 16; k++) {
+        for (u32 k = 0; k < NC; k++) {
             u32 h; bool ok;
             u64* p = blk_ptr(k, ok, h);
-            sm[tid * CT_PITCH + k] = ok ? p[tid] : 0ull;
+#pragma unroll
+            for (u32 u = tid; u < 256; u += TH) sm[K::idx(u, k)] = ok ? p[u] : 0ull;
         }
         __syncthreads();
         {
-            u32 c = tid & 15, uhi = tid >> 4, h; bool ok;
+            u32 c = tid & (NC - 1), uhi = tid >> LB, h; bool ok;
             (void)blk_ptr(c, ok, h);
             u64 x[16];
 #pragma unroll
-            for (int e = 0; e < 16; e++) x[e] = sm[(uhi * 16 + e) * CT_PITCH + c];
+            for (int e = 0; e < 16; e++) x[e] = sm[K::idx(uhi * 16 + e, c)];
             inv_step<4, 1, INV_NORM>(x, tw, ((N1 + h) << 4) + uhi, Q, nq);
 #pragma unroll
-            for (int e = 0; e < 16; e++) sm[(uhi * 16 + e) * CT_PITCH + c] = x[e];
+            for (int e = 0; e < 16; e++) sm[K::idx(uhi * 16 + e, c)] = x[e];
         }
         __syncthreads();
         {
@@ -357,7 +381,7 @@ ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
             u64* p = blk_ptr(c, ok, h);
             u64 x[16];
 #pragma unroll
-            for (int e = 0; e < 16; e++) x[e] = sm[(e * 16 + ulow) * CT_PITCH + c];
+            for (int e = 0; e < 16; e++) x[e] = sm[K::idx(e * 16 + ulow, c)];
             inv_step<4, INV_NORM, INV_NORM>(x, tw, N1 + h, Q, nq);
             if (ok) {
 #pragma unroll
@@ -418,57 +442,86 @@ ntt_small_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
 // ------------------------------------------------------------------------------------------
 // Launchers
 // ------------------------------------------------------------------------------------------
-template <int RL, bool INV>
+// log2(coefficients per tile) of the strided (which = 0) and contig (which = 1) pass.  The defaults
+// can be overridden for tuning: FHE_B200_NTT_TILE_S / FHE_B200_NTT_TILE_C = 9 | 10 | 11 | 12.
+static int tile_log(int which) {
+    static int tl[2] = {0, 0};
+    if (!tl[which]) {
+        const char* e = getenv(which ? "FHE_B200_NTT_TILE_C" : "FHE_B200_NTT_TILE_S");
+        int v = e ? atoi(e) : 0;
+        tl[which] = (v >= 9 && v <= 12) ? v : NTT_TILE_LOG_DEFAULT[which];
+    }
+    return tl[which];
+}
+
+template <int RL, int TL, bool INV>
 static cudaError_t launch_strided_t(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
-    using K = StridedCfg<RL>;
+    using K = StridedCfg<RL, TL>;
     static bool attr_done = false;
     if (!attr_done && K::SMEM > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(ntt_strided_kernel<RL, INV>,
+        cudaError_t e = cudaFuncSetAttribute(ntt_strided_kernel<RL, TL, INV>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
     size_t grid = batch * r.T * (256 / K::C);
-    ntt_strided_kernel<RL, INV><<<(unsigned)grid, K::THREADS, K::SMEM, st>>>(
+    ntt_strided_kernel<RL, TL, INV><<<(unsigned)grid, K::THREADS, K::SMEM, st>>>(
         data, INV ? r.twI : r.twF, r.mods, r.invc, r.T, r.logN);
     kernel_launch_count_add(1);
     return cudaGetLastError();
 }
 
+template <int RL, bool INV>
+static cudaError_t launch_strided_rl(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
+    if constexpr (RL >= 4) {                       // smaller rings: the tile is already below 4096 coefficients
+        switch (tile_log(0)) {
+            case 9:  if constexpr (RL >= 7) return launch_strided_t<RL, 9, INV>(r, data, batch, st);
+            case 10: if constexpr (RL >= 6) return launch_strided_t<RL, 10, INV>(r, data, batch, st);
+            case 11: if constexpr (RL >= 5) return launch_strided_t<RL, 11, INV>(r, data, batch, st);
+        }
+    }
+    return launch_strided_t<RL, 12, INV>(r, data, batch, st);
+}
+
 template <bool INV>
 static cudaError_t launch_strided(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
     switch (r.logN - 8) {
-        case 1: return launch_strided_t<1, INV>(r, data, batch, st);
-        case 2: return launch_strided_t<2, INV>(r, data, batch, st);
-        case 3: return launch_strided_t<3, INV>(r, data, batch, st);
-        case 4: return launch_strided_t<4, INV>(r, data, batch, st);
-        case 5: return launch_strided_t<5, INV>(r, data, batch, st);
-        case 6: return launch_strided_t<6, INV>(r, data, batch, st);
-        case 7: return launch_strided_t<7, INV>(r, data, batch, st);
-        case 8: return launch_strided_t<8, INV>(r, data, batch, st);
+        case 1: return launch_strided_rl<1, INV>(r, data, batch, st);
+        case 2: return launch_strided_rl<2, INV>(r, data, batch, st);
+        case 3: return launch_strided_rl<3, INV>(r, data, batch, st);
+        case 4: return launch_strided_rl<4, INV>(r, data, batch, st);
+        case 5: return launch_strided_rl<5, INV>(r, data, batch, st);
+        case 6: return launch_strided_rl<6, INV>(r, data, batch, st);
+        case 7: return launch_strided_rl<7, INV>(r, data, batch, st);
+        case 8: return launch_strided_rl<8, INV>(r, data, batch, st);
     }
     return cudaErrorInvalidValue;
+}
+
+template <int LB, bool INV>
+static cudaError_t launch_contig_t(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
+    using K = ContigCfg<LB>;
+    const u32 N1 = r.N >> 8, NC = K::NC;
+    u32 logCB = 0;                                   // batch items per tile: largest 2^k <= min(batch, NC) ...
+    while (logCB < (u32)LB && (2u << logCB) <= batch) logCB++;
+    while ((NC >> logCB) > N1) logCB++;              // ... but never more blocks per tile than the ring has
+    const u32 CB = 1u << logCB, CH = NC >> logCB;
+    size_t grid = (size_t)r.T * ((batch + CB - 1) / CB) * (N1 / CH);
+    ntt_contig_kernel<LB, INV><<<(unsigned)grid, K::THREADS, K::SMEM, st>>>(data, INV ? r.twI : r.twF, r.mods,
+                                                                          r.T, r.logN, (u32)batch, logCB);
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
 }
 
 template <bool INV>
 static cudaError_t launch_contig(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
     const u32 N1 = r.N >> 8;
-    u32 logCB = 0;                                   // batch items per tile: largest 2^k <= min(batch,16) ...
-    while (logCB < 4 && (2u << logCB) <= batch) logCB++;
-    while ((16u >> logCB) > N1) logCB++;             // ... but never more blocks per tile than the ring has
-    const u32 CB = 1u << logCB, CH = 16u >> logCB;
-    size_t grid = (size_t)r.T * ((batch + CB - 1) / CB) * (N1 / CH);
-    static bool attr_done[2] = {false, false};
-    if (!attr_done[INV]) {
-        cudaError_t e = cudaFuncSetAttribute(ntt_contig_kernel<INV>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM);
-        if (e != cudaSuccess) return e;
-        attr_done[INV] = true;
+    switch (tile_log(1)) {
+        case 9:  return launch_contig_t<1, INV>(r, data, batch, st);
+        case 10: if (N1 >= 4 || batch >= 4) return launch_contig_t<2, INV>(r, data, batch, st);
+        case 11: if (N1 >= 8 || batch >= 8) return launch_contig_t<3, INV>(r, data, batch, st);
     }
-    ntt_contig_kernel<INV><<<(unsigned)grid, 256, CT_SMEM, st>>>(data, INV ? r.twI : r.twF, r.mods,
-                                                                 r.T, r.logN, (u32)batch, logCB);
-    kernel_launch_count_add(1);
-    return cudaGetLastError();
+    return launch_contig_t<4, INV>(r, data, batch, st);
 }
 
 template <bool INV>
