@@ -108,6 +108,8 @@ def test_twiddle_tables_vs_oracle(pkg, backend, oracle, n, nbits):
     (1, 1, 1, 10), (2, 2, 3, 12), (3, 2, 1, 22), (5, 1, 2, 30), (8, 3, 2, 60),
     (9, 2, 3, 60), (10, 1, 1, 60), (11, 3, 17, 55), (12, 2, 16, 60), (13, 2, 5, 60),
     (14, 2, 2, 60), (14, 4, 33, 60), (15, 3, 4, 60), (16, 2, 3, 60), (16, 3, 16, 60), (16, 1, 1, 60),
+    # two-pass kernels with short moduli (range tracking and the float quotient estimate at every size)
+    (9, 2, 4, 14), (10, 2, 3, 20), (11, 2, 2, 25), (12, 2, 2, 33), (13, 1, 2, 41), (14, 1, 2, 48), (16, 1, 1, 21),
 ])
 def test_ntt_vs_oracle(pkg, backend, oracle, logn, towers, batch, nbits):
     n = 1 << logn
@@ -130,6 +132,28 @@ def test_ntt_vs_oracle(pkg, backend, oracle, logn, towers, batch, nbits):
     e = pkg.DCRTPolyBatch(ring, batch, pkg.EVALUATION, y)
     e.SwitchFormat()
     assert np.array_equal(e.to_host(), octx.ntt(y, inverse=True)), "inverse"
+    ring.close()
+
+
+@pytest.mark.parametrize("logn,nbits", [(9, 60), (12, 60), (14, 60), (16, 60), (16, 59), (13, 30)])
+def test_ntt_extreme_values(pkg, backend, oracle, logn, nbits):
+    """Inputs that push the lazily reduced intermediates to the top of their ranges: all q-1, alternating
+    q-1 / 0, a single q-1 — forward and inverse, against the oracle."""
+    n = 1 << logn
+    q, psi = params(oracle, nbits, n, 2)
+    octx = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q, psi)
+    x = np.zeros((4, 2, n), np.uint64)
+    x[0] = (q - 1)[:, None]
+    x[1, :, ::2] = (q - 1)[:, None]
+    x[2, :, 1::2] = (q - 1)[:, None]
+    x[3, :, n // 2] = q - 1
+    for fmt, inv in ((pkg.COEFFICIENT, False), (pkg.EVALUATION, True)):
+        d = pkg.DCRTPolyBatch(ring, 4, fmt, x)
+        d.SwitchFormat()
+        got = d.to_host()
+        assert np.array_equal(got, octx.ntt(x, inverse=inv))
+        assert (got < q[None, :, None]).all()
     ring.close()
 
 

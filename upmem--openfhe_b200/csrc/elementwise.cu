@@ -124,7 +124,7 @@ static TowerMod make_mod_host(uint64_t q) {
     m.mu = (uint64_t)(((unsigned __int128)1 << (2 * msb + 3)) / q);
     m.n = msb - 2;
     m.s = msb + 5;
-    m.pad = 0;
+    towermod_set_reduce(m);
     return m;
 }
 

@@ -21,8 +21,19 @@ struct __align__(32) TowerMod {
     u64 mu;       // floor(2^(2*msb(q)+3) / q)          (ComputeMu, ubintnat.h:650-656)
     u32 n;        // msb(q) - 2                          (first Barrett shift)
     u32 s;        // n + 7                               (second Barrett shift)
-    u64 pad;
+    u32 rsh;      // range reduction: shift that brings 16q below 2^24 ...
+    float rinv;   // ... and a rounded-DOWN reciprocal of (q >> rsh) (+1 if rsh > 0)
 };
+
+// Host-side fill of the range-reduction constants (used by runtime.cu / elementwise.cu).
+inline void towermod_set_reduce(TowerMod& m) {
+    unsigned bits = m.q ? 64u - (unsigned)__builtin_clzll(m.q) : 0u;
+    m.rsh = bits + 4 > 24 ? bits + 4 - 24 : 0;
+    double d = (double)((m.q >> m.rsh) + (m.rsh ? 1 : 0));
+    float r = (float)(1.0 / d);
+    while ((double)r * d > 1.0) r = __builtin_nextafterf(r, 0.0f);
+    m.rinv = r;
+}
 
 __device__ __forceinline__ u64 addmod(u64 a, u64 b, u64 q) {
     u64 r = a + b;
@@ -108,6 +119,16 @@ __device__ __forceinline__ u64 reduce_range(u64 x, const QMul& Q) {
         constexpr int NEXT = (FROM - M) > M ? (FROM - M) : M;
         return reduce_range<NEXT, TO>(csub(x, qm<M>(Q)), Q);
     }
+}
+
+// v in [0,16q) -> [0,q) with one quotient estimate instead of four conditional subtractions:
+// k = floor(float(v >> rsh) * rinv) never exceeds floor(v/q) and is at most one short of it (the
+// operands are below 2^24, hence exact in fp32; rinv and the product are rounded towards zero), so
+// v - k*q is in [0,2q).  kq = shared table {0, q, 2q, .., 15q}.  Conversions run on the XU pipe, the
+// table read on the LSU: neither touches the integer-multiply pipe the butterflies are bound by.
+__device__ __forceinline__ u64 reduce16(u64 v, const u64* kq, u32 rsh, float rinv, u64 q) {
+    u32 k = __float2uint_rz(__fmul_rz(__uint2float_rz((u32)(v >> rsh)), rinv));
+    return csub(v - kq[k], q);
 }
 
 // Forward (Cooley-Tukey): X in [0,Bq), Y anything below 2^64 -> both in [0,(B+2)q).  No reduction of X.

@@ -102,6 +102,7 @@ cudaError_t launch_modop(int kind, uint64_t* dst, const uint64_t* src, size_t n,
         tm.mu = (uint64_t)(((unsigned __int128)1 << (2 * msb + 3)) / mod);
         tm.n = msb - 2;
         tm.s = msb + 5;
+        towermod_set_reduce(tm);
     }
     size_t blocks = (n + 255) / 256;
     if (blocks > 148 * 32) blocks = 148 * 32;

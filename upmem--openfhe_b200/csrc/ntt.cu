@@ -311,10 +311,13 @@ ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
     const u32 hg = bid % hgroups; bid /= hgroups;
     const u32 bg = bid % bgroups;
     const u32 tower = bid / bgroups;
-    const u64 q = mods[tower].q, nq = 0ull - q;
+    const TowerMod tm = mods[tower];
+    const u64 q = tm.q, nq = 0ull - q;
     const QMul Q = make_qmul(q);
     const ulonglong2* tw = twAll + ((size_t)tower << logN);
     const u32 tid = threadIdx.x;
+    u64* kq = sm + K::SMEM / 8;                        // {0, q, .., 15q} for the closing range reduction
+    if (!INV && tid < 16) kq[tid] = tid * q;           // visible after the first barrier
 
     auto blk_ptr = [&](u32 c, bool& ok, u32& h) -> u64* {
         u32 b = bg * CB + (c & (CB - 1));
@@ -344,7 +347,7 @@ ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
             fwd_step<4, FwdStep<4, MAXB>::OUT>(x, tw, ((N1 + h) << 4) + uhi, Q, nq);
 #pragma unroll
             for (int e = 0; e < 16; e++)
-                sm[K::idx(uhi * 16 + e, c)] = reduce_range<FwdStep<4, FwdStep<4, MAXB>::OUT>::OUT, 1>(x[e], Q);
+                sm[K::idx(uhi * 16 + e, c)] = reduce16(x[e], kq, tm.rsh, tm.rinv, q);
         }
         __syncthreads();
 #pragma unroll
@@ -507,7 +510,7 @@ static cudaError_t launch_contig_t(const RingDev& r, u64* data, size_t batch, cu
     while ((NC >> logCB) > N1) logCB++;              // ... but never more blocks per tile than the ring has
     const u32 CB = 1u << logCB, CH = NC >> logCB;
     size_t grid = (size_t)r.T * ((batch + CB - 1) / CB) * (N1 / CH);
-    ntt_contig_kernel<LB, INV><<<(unsigned)grid, K::THREADS, K::SMEM, st>>>(data, INV ? r.twI : r.twF, r.mods,
+    ntt_contig_kernel<LB, INV><<<(unsigned)grid, K::THREADS, K::SMEM + 128, st>>>(data, INV ? r.twI : r.twF, r.mods,
                                                                           r.T, r.logN, (u32)batch, logCB);
     kernel_launch_count_add(1);
     return cudaGetLastError();

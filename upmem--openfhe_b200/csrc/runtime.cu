@@ -374,7 +374,7 @@ static TowerMod make_mod(uint64_t q) {
     m.mu = (uint64_t)(((host::u128)1 << (2 * b + 3)) / q);
     m.n = b - 2;
     m.s = b + 5;
-    m.pad = 0;
+    towermod_set_reduce(m);
     return m;
 }
 
