@@ -130,6 +130,20 @@ int fhe_ntt_algo(fhe_ring* ring, fhe_dptr x, size_t batch, int inverse, int algo
 /* c = INTT(NTT(a) .* NTT(b)): negacyclic product of COEFFICIENT-format polynomials; a and b are
  * left in EVALUATION format (they are transformed in place), c may alias neither. */
 int fhe_poly_mul(fhe_ring* ring, fhe_dptr c, fhe_dptr a, fhe_dptr b, size_t batch, int stream);
+/* Ciphertext tensor product, 2 x 2 case of LeveledSHEBase::EvalMultCore
+ * (src/pke/lib/schemebase/base-leveledshe.cpp:667-672): with a = (a[0], a[1]), b = (b[0], b[1]) batches of
+ * DCRTPolys in EVALUATION format, c[0] = a0*b0, c[1] = a1*b0 + a0*b1, c[2] = a1*b1, one fused launch
+ * (56 B of HBM traffic per coefficient slot instead of 120 B for four Times and one +=).  The three
+ * outputs must be distinct buffers; an output may be the same buffer as an input. */
+int fhe_ct_tensor_product(fhe_ring* ring, const fhe_dptr* c, const fhe_dptr* a, const fhe_dptr* b, size_t batch,
+                          int stream);
+/* The multiplication pipelines BASELINE.json's configs 4 and 5 are worded as, composed from the calls
+ * above.  transform 0: tensor product only.  1: forward NTT of the four inputs (in place, they stay in
+ * EVALUATION format), tensor product, inverse NTT of the three outputs (COEFFICIENT in, COEFFICIENT
+ * out: the primitive part of BFVrns EvalMult, bfvrns-leveledshe.cpp:193-343).  2: inverse NTT of the
+ * inputs, tensor product, forward NTT of the outputs (config 4's wording). */
+int fhe_ct_multiply(fhe_ring* ring, const fhe_dptr* c, const fhe_dptr* a, const fhe_dptr* b, size_t batch,
+                    int transform, int stream);
 /* seeded uniform coefficients in [0, q_tower) (synthetic inputs for tests and benchmarks) */
 int fhe_fill_uniform(fhe_ring* ring, fhe_dptr dst, size_t batch, uint64_t seed, int stream);
 

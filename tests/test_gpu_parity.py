@@ -308,3 +308,57 @@ def test_cpp_pim_surface_binary():
         subprocess.check_call(["make", "-C", root, "host"])
     r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "all ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+# ---- ciphertext tensor product and the multiplication pipelines (BASELINE configs 4 and 5) --------------
+def _oracle_tensor(octx, a0, a1, b0, b1):
+    """LeveledSHEBase::EvalMultCore, 2x2 case (base-leveledshe.cpp:667-672), op by op on the oracle."""
+    c2 = octx.elementwise(MUL, a1, b1)
+    c1 = octx.elementwise(MUL, a1, b0)
+    c0 = octx.elementwise(MUL, b0, a0)
+    c1 = octx.elementwise(ADD, c1, octx.elementwise(MUL, a0, b1))
+    return c0, c1, c2
+
+
+@pytest.mark.parametrize("n,towers,batch,nbits", [(4, 3, 1, 14), (512, 2, 3, 30), (1 << 12, 3, 2, 60), (1 << 14, 4, 3, 60),
+                                                   (1 << 16, 2, 1, 60)])
+@pytest.mark.parametrize("transform", [0, 1, 2])
+def test_ct_multiply_vs_oracle(pkg, backend, oracle, n, towers, batch, nbits, transform):
+    q, psi = params(oracle, nbits, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q, psi)
+    rng = np.random.default_rng(n + transform)
+    host = [rand_polys(rng, batch, n, q) for _ in range(4)]
+    host[0][0, :, :2] = (q - 1)[:, None]
+    host[2][0, :, :2] = (q - 1)[:, None]
+    fmt = pkg.EVALUATION if transform != 1 else pkg.COEFFICIENT
+    dev = [pkg.DCRTPolyBatch(ring, batch, fmt, h) for h in host]
+    out = [pkg.DCRTPolyBatch(ring, batch, fmt) for _ in range(3)]
+    ring.ct_multiply([o.dptr for o in out], [dev[0].dptr, dev[1].dptr], [dev[2].dptr, dev[3].dptr], batch, transform)
+    x = host
+    if transform:
+        x = [octx.ntt(h, inverse=(transform == 2)) for h in host]
+    exp = _oracle_tensor(octx, *x)
+    if transform:
+        exp = [octx.ntt(e, inverse=(transform == 1)) for e in exp]
+    for o, e in zip(out, exp):
+        assert np.array_equal(o.to_host(), e)
+    ring.close()
+
+
+def test_ct_multiply_in_place_and_squaring(pkg, backend, oracle):
+    n, towers, batch = 1 << 13, 2, 2
+    q, psi = params(oracle, 60, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q, psi)
+    rng = np.random.default_rng(99)
+    a0, a1 = rand_polys(rng, batch, n, q), rand_polys(rng, batch, n, q)
+    d0, d1 = pkg.DCRTPolyBatch(ring, batch, pkg.EVALUATION, a0), pkg.DCRTPolyBatch(ring, batch, pkg.EVALUATION, a1)
+    d2 = pkg.DCRTPolyBatch(ring, batch, pkg.EVALUATION)
+    # square a ciphertext, writing c0 over a0 and c1 over a1
+    ring.ct_multiply([d0.dptr, d1.dptr, d2.dptr], [d0.dptr, d1.dptr], [d0.dptr, d1.dptr], batch, 0)
+    e0, e1, e2 = _oracle_tensor(octx, a0, a1, a0, a1)
+    assert np.array_equal(d0.to_host(), e0) and np.array_equal(d1.to_host(), e1) and np.array_equal(d2.to_host(), e2)
+    with pytest.raises(pkg.FheError):
+        ring.ct_multiply([d0.dptr, d0.dptr, d2.dptr], [d0.dptr, d1.dptr], [d0.dptr, d1.dptr], batch, 0)
+    ring.close()

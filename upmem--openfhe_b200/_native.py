@@ -49,6 +49,8 @@ SIGNATURES = {
     "fhe_ntt_inverse": (ci, [vp, u64, sz, ci]),
     "fhe_ntt_algo": (ci, [vp, u64, sz, ci, ci, ci]),
     "fhe_poly_mul": (ci, [vp, u64, u64, u64, sz, ci]),
+    "fhe_ct_tensor_product": (ci, [vp, pu64, pu64, pu64, sz, ci]),
+    "fhe_ct_multiply": (ci, [vp, pu64, pu64, pu64, sz, ci, ci]),
     "fhe_fill_uniform": (ci, [vp, u64, sz, u64, ci]),
     "fhe_vec_op": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),
     "fhe_vec_op_scalar": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),

@@ -537,6 +537,43 @@ extern "C" int fhe_poly_mul(fhe_ring* r, fhe_dptr c, fhe_dptr a, fhe_dptr b, siz
     return fhe_ntt_inverse(r, c, batch, stream);
 }
 
+extern "C" int fhe_ct_tensor_product(fhe_ring* r, const fhe_dptr* c, const fhe_dptr* a, const fhe_dptr* b,
+                                     size_t batch, int stream) {
+    cudaStream_t s;
+    int rc = ring_stream(r, stream, &s);
+    if (rc) return rc;
+    if (!c || !a || !b) return fail(FHE_EINVAL, "fhe_ct_tensor_product: null argument");
+    if (batch == 0) return FHE_OK;
+    if (!c[0] || !c[1] || !c[2] || !a[0] || !a[1] || !b[0] || !b[1])
+        return fail(FHE_EINVAL, "fhe_ct_tensor_product: null device pointer");
+    if (c[0] == c[1] || c[0] == c[2] || c[1] == c[2]) return fail(FHE_EINVAL, "fhe_ct_tensor_product: outputs must be distinct");
+    if (r->dev.N == 1 && ((batch * r->dev.T) & 1)) return fail(FHE_EUNSUPPORTED, "fhe_ct_tensor_product: N=1 needs an even number of towers*batch");
+    auto P = [](fhe_dptr p) { return (uint64_t*)(uintptr_t)p; };
+    CUDA_TRY(launch_tensor_product(r->dev, P(c[0]), P(c[1]), P(c[2]), P(a[0]), P(a[1]), P(b[0]), P(b[1]), batch, s));
+    return FHE_OK;
+}
+
+extern "C" int fhe_ct_multiply(fhe_ring* r, const fhe_dptr* c, const fhe_dptr* a, const fhe_dptr* b, size_t batch,
+                               int transform, int stream) {
+    if (transform < 0 || transform > 2) return fail(FHE_EINVAL, "fhe_ct_multiply: transform must be 0, 1 or 2");
+    if (!c || !a || !b) return fail(FHE_EINVAL, "fhe_ct_multiply: null argument");
+    int rc;
+    if (transform) {
+        const int inv_in = transform == 2;       // 1: NTT in, INTT out;  2: INTT in, NTT out
+        const fhe_dptr in[4] = {a[0], a[1], b[0], b[1]};
+        for (int i = 0; i < 4; i++) {
+            bool seen = false;                   // squaring passes the same buffers twice: transform once
+            for (int j = 0; j < i; j++) seen |= in[j] == in[i];
+            if (!seen && (rc = fhe_ntt_algo(r, in[i], batch, inv_in, 0, stream))) return rc;
+        }
+    }
+    if ((rc = fhe_ct_tensor_product(r, c, a, b, batch, stream))) return rc;
+    if (transform)
+        for (int i = 0; i < 3; i++)
+            if ((rc = fhe_ntt_algo(r, c[i], batch, transform == 1, 0, stream))) return rc;
+    return FHE_OK;
+}
+
 extern "C" int fhe_fill_uniform(fhe_ring* r, fhe_dptr dst, size_t batch, uint64_t seed, int stream) {
     cudaStream_t s;
     int rc = ring_stream(r, stream, &s);

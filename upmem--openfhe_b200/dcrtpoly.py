@@ -149,6 +149,12 @@ class Ring:
     def poly_mul(self, c, a, b, batch, stream=0):
         N.check(N.lib.fhe_poly_mul(self.h, c, a, b, batch, stream))
 
+    def ct_multiply(self, c, a, b, batch, transform=0, stream=0):
+        """c (3 device pointers) = tensor product of ciphertext batches a, b (2 pointers each);
+        transform as fhe_ct_multiply: 0 none, 1 NTT in / INTT out, 2 INTT in / NTT out."""
+        arr = lambda ps: (ctypes.c_uint64 * len(ps))(*ps)
+        N.check(N.lib.fhe_ct_multiply(self.h, arr(c), arr(a), arr(b), batch, transform, stream))
+
     def fill_uniform(self, dst, batch, seed, stream=0):
         N.check(N.lib.fhe_fill_uniform(self.h, dst, batch, seed, stream))
 
