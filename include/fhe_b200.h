@@ -160,6 +160,11 @@ int fhe_vec_op_scalar(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, uint64_t s
 int fhe_vec_modop(fhe_ctx* ctx, int kind, fhe_dptr dst, fhe_dptr src, size_t n, uint64_t mod, uint64_t p,
                   uint64_t q, int stream);
 
+/* Order-independent digest of nwords device words: sum_xor[0] = sum mod 2^64, sum_xor[1] = xor.
+ * Digests of shards add up (sum) / xor together to the digest of the whole, so sharded results can be
+ * compared without gathering them.  Blocking. */
+int fhe_checksum(fhe_ctx* ctx, fhe_dptr src, size_t nwords, uint64_t* sum_xor, int stream);
+
 /* ---- legacy descriptor path ------------------------------------------------------------------ */
 /* desc points to a `struct mod_add_sub_mult` (pim/common.h:23-30) whose operands are byte offsets
  * from `heap_base` and byte sizes; kernel_id picks add / sub / mult; for FHE_KERNEL_MOD_OPS desc

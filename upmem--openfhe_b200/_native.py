@@ -55,6 +55,7 @@ SIGNATURES = {
     "fhe_vec_op": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),
     "fhe_vec_op_scalar": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),
     "fhe_vec_modop": (ci, [vp, ci, u64, u64, sz, u64, u64, u64, ci]),
+    "fhe_checksum": (ci, [vp, u64, sz, pu64, ci]),
     "fhe_launch": (ci, [vp, ci, vp, u64]),
     "fhe_dcrt_op_host": (ci, [vp, ci, vp, vp, vp, sz]),
     "fhe_dcrt_multi_op_host": (ci, [vp, ctypes.POINTER(ci), ci, ctypes.POINTER(vp), vp, vp, sz]),

@@ -282,6 +282,37 @@ cudaError_t launch_vec_scalar(int op, uint64_t* dst, const uint64_t* a, uint64_t
     return cudaErrorInvalidValue;
 }
 
+// ---- order-independent digest of a buffer: (sum mod 2^64, xor) -----------------------------------
+// Lets sharded results be compared without gathering them (config 4's results stay
+// sharded, "only a checksum/sample is gathered"); matches sharding.checksum on the host.
+__global__ void __launch_bounds__(256)
+checksum_kernel(const u64* __restrict__ x, size_t n, u64* __restrict__ out) {
+    u64 s = 0, xr = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        u64 v = x[i];
+        s += v; xr ^= v;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        xr ^= __shfl_xor_sync(0xffffffffu, xr, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(out, s);
+        atomicXor(out + 1, xr);
+    }
+}
+
+cudaError_t launch_checksum(const uint64_t* x, size_t n, uint64_t* out2, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(out2, 0, 16, st);
+    if (e != cudaSuccess || n == 0) return e;
+    size_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    checksum_kernel<<<(unsigned)blocks, 256, 0, st>>>(reinterpret_cast<const u64*>(x), n, reinterpret_cast<u64*>(out2));
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
+}
+
 // ---- seeded uniform fill: value i of tower t depends only on (seed, i, q_t) ----
 __device__ __forceinline__ u64 splitmix64(u64 z) {
     z += 0x9E3779B97F4A7C15ull;

@@ -44,6 +44,8 @@ cudaError_t launch_fill_uniform(const RingDev& r, uint64_t* dst, size_t batch, u
 // when ModInverse meets an element without an inverse.
 cudaError_t launch_modop(int kind, uint64_t* dst, const uint64_t* src, size_t n, uint64_t mod, uint64_t p,
                          uint64_t q, int* err, cudaStream_t st);
+// out2[0] = sum of the n words mod 2^64, out2[1] = their xor (out2 is device memory, 16 bytes).
+cudaError_t launch_checksum(const uint64_t* x, size_t n, uint64_t* out2, cudaStream_t st);
 // Integer-pipe probe: every thread runs `iters` dependent-chain-free 64x64->128 multiply-adds.
 cudaError_t launch_imad_probe(uint64_t* out, int blocks, int threads, int iters, cudaStream_t st);
 

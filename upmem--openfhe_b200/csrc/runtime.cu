@@ -655,6 +655,23 @@ extern "C" int fhe_vec_op_scalar(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a,
     return FHE_OK;
 }
 
+extern "C" int fhe_checksum(fhe_ctx* ctx, fhe_dptr src, size_t nwords, uint64_t* sum_xor, int stream) {
+    cudaStream_t s;
+    int rc = get_stream(ctx, stream, &s);
+    if (rc) return rc;
+    if (!sum_xor) return fail(FHE_EINVAL, "fhe_checksum: null output");
+    if (nwords && !src) return fail(FHE_EINVAL, "fhe_checksum: null device pointer");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    void* d = nullptr;
+    if ((rc = ctx->arena.alloc(256, &d))) return rc;
+    cudaError_t e = launch_checksum((const uint64_t*)(uintptr_t)src, nwords, (uint64_t*)d, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sum_xor, d, 16, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    ctx->arena.release(d);
+    if (e != cudaSuccess) return fail(FHE_ECUDA, "fhe_checksum: %s", cudaGetErrorString(e));
+    return FHE_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // legacy descriptor path (PimData::common_do_ops, pim/PimData.h:275-305)
 // ---------------------------------------------------------------------------------------------

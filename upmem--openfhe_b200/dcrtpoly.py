@@ -106,6 +106,12 @@ class Backend:
         """kind: enum mod_kernel of pim/common.h (0 SWITCHMODULUS .. 12 DIVIDEANDROUNDEQ)."""
         N.check(N.lib.fhe_vec_modop(self.h, kind, dst, src, n, int(mod), int(p), int(q), stream))
 
+    def checksum(self, dptr, nwords, stream=0):
+        """(sum mod 2^64, xor) of a device buffer; equals sharding.checksum of the same words."""
+        out = (ctypes.c_uint64 * 2)()
+        N.check(N.lib.fhe_checksum(self.h, dptr, nwords, out, stream))
+        return int(out[0]), int(out[1])
+
     def imad_probe(self, blocks, threads, iters):
         ms = ctypes.c_float()
         N.check(N.lib.fhe_imad_probe(self.h, blocks, threads, iters, ctypes.byref(ms)))
