@@ -333,6 +333,33 @@ def ntt_extra(pkg, be):
                         "frac_of_measured_peak": 32 * words / (f_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}}
             be.free(x)
             ring.close()
+        # ciphertext multiplication pipelines (BASELINE configs[3] / configs[4] shapes, batch cut to fit a short run)
+        for name, logn, towers, batch, transform in (("ct_tensor_n65536_t40_b32", 16, 40, 32, 0),
+                                                     ("ct_mul_pipeline_cfg4_n65536_t40_b32", 16, 40, 32, 2),
+                                                     ("ct_mul_pipeline_cfg5_n32768_t16_b128", 15, 16, 128, 1)):
+            n = 1 << logn
+            q, psi = pkg.gen_params(60, n, towers)
+            ring = pkg.Ring(be, n, q, psi)
+            words = ring.words(batch)
+            bufs = [be.alloc(words * 8) for _ in range(7)]
+            for i in range(4):
+                ring.fill_uniform(bufs[i], batch, 20260010 + i)
+            args = (bufs[4:7], bufs[0:2], bufs[2:4], batch, transform)
+            for _ in range(2):
+                ring.ct_multiply(*args)
+            be.sync()
+            reps = 5
+            be.timer_start(0)
+            for _ in range(reps):
+                ring.ct_multiply(*args)
+            ms = be.timer_stop(0) / reps
+            ops_per_slot = 5 + (7 if transform else 0)          # 4 mul + 1 add (+ 4 + 3 transforms)
+            out[name] = {"ms": ms, "ciphertext_products_per_s": batch / (ms * 1e-3),
+                         "coeff_ops_per_s": ops_per_slot * words / (ms * 1e-3), "coeff_ops_per_slot": ops_per_slot,
+                         "hbm_gbs_tensor_only": (56 * words / (ms * 1e-3) / 1e9) if not transform else None}
+            for b_ in bufs:
+                be.free(b_)
+            ring.close()
     except Exception as ex:
         out["error"] = str(ex)[:300]
     return out
