@@ -15,6 +15,7 @@
 #include <cstdint>
 #include <cstring>
 #include <memory>
+#include <string>
 #include <vector>
 #include <omp.h>
 
@@ -29,7 +30,32 @@ struct ref_polys {
     std::vector<DCRTPoly> v;
 };
 
+static thread_local std::string g_ref_err;
+
 extern "C" {
+
+const char* ref_last_error(void) { return g_ref_err.c_str(); }
+
+// Live intercept (only in the hooked build, oracle/Makefile `hooked`): attach / detach the backend handle
+// the way src/pke/examples/simple-integers.cpp:120-130 sketches, DCRTPolyImpl::SetPim (dcrtpoly.h:410-417).
+// Returns 0, 1 on failure (message in ref_last_error), -1 when this build has no hook.
+int ref_polys_set_pim(ref_polys* p, int on) {
+#ifdef FHE_HOOKED
+    try {
+        std::shared_ptr<PimManager> h;
+        if (on) h = std::shared_ptr<PimManager>(PimManager::getPim(4), [](PimManager*) {});
+        for (auto& poly : p->v) poly.SetPim(h);
+        return 0;
+    }
+    catch (const std::exception& e) {
+        g_ref_err = e.what();
+        return 1;
+    }
+#else
+    (void)p; (void)on;
+    return -1;
+#endif
+}
 
 // poly-benchmark-16k.cpp:82-101
 void ref_gen_params(uint32_t nbits, uint32_t N, uint32_t T, uint64_t* q, uint64_t* psi) {
@@ -106,10 +132,16 @@ double ref_polys_op(ref_polys* a, const ref_polys* b, int op, int outer_threads)
     size_t B = a->v.size();
     auto t0  = std::chrono::steady_clock::now();
     if (outer_threads <= 1) {
-        for (size_t i = 0; i < B; i++) {
-            if (op == 0) a->v[i] += b->v[i];
-            else if (op == 1) a->v[i] -= b->v[i];
-            else a->v[i] *= b->v[i];
+        try {
+            for (size_t i = 0; i < B; i++) {
+                if (op == 0) a->v[i] += b->v[i];
+                else if (op == 1) a->v[i] -= b->v[i];
+                else a->v[i] *= b->v[i];
+            }
+        }
+        catch (const std::exception& e) {     // the hooked build throws when the backend fails (no CPU fallback)
+            g_ref_err = e.what();
+            return -1.0;
         }
     }
     else {
@@ -128,7 +160,13 @@ double ref_polys_switch_format(ref_polys* a, int outer_threads) {
     size_t B = a->v.size();
     auto t0  = std::chrono::steady_clock::now();
     if (outer_threads <= 1) {
-        for (size_t i = 0; i < B; i++) a->v[i].SwitchFormat();
+        try {
+            for (size_t i = 0; i < B; i++) a->v[i].SwitchFormat();
+        }
+        catch (const std::exception& e) {
+            g_ref_err = e.what();
+            return -1.0;
+        }
     }
     else {
 #pragma omp parallel for num_threads(outer_threads) schedule(static)

@@ -1,0 +1,107 @@
+"""the intercept LIVE inside the reference.  oracle/_ref/libopenfhe_hooked.so is the
+reference's own DCRTPolyImpl / PolyImpl / NativeVector compiled against include/pim/*.h of this repository
+with the four intercept calls patched in (oracle/hook_patch.py).  With a handle attached through the
+reference's own SetPim, DCRTPoly += / -= / *= and SwitchFormat run on the B200; results must equal the
+CPU path bit for bit.  The library is built where /root/reference exists and travels to the GPU box."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+from tests import oracle_py
+
+HOOKED_SO = os.path.join(os.path.dirname(oracle_py.REF_SO), "libopenfhe_hooked.so")
+pytestmark = pytest.mark.skipif(not os.path.exists(HOOKED_SO), reason="oracle/_ref/libopenfhe_hooked.so not built")
+vp, sz, ci, u32, u64 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint32, ctypes.c_uint64
+
+
+@pytest.fixture(scope="module")
+def hooked():
+    H = ctypes.CDLL(HOOKED_SO)
+    H.ref_ctx_create.restype = vp
+    H.ref_ctx_create.argtypes = [u32, u32, vp, vp]
+    H.ref_ctx_destroy.argtypes = [vp]
+    H.ref_polys_load.restype = vp
+    H.ref_polys_load.argtypes = [vp, vp, sz, ci]
+    H.ref_polys_store.argtypes = [vp, vp]
+    H.ref_polys_free.argtypes = [vp]
+    H.ref_polys_op.restype = ctypes.c_double
+    H.ref_polys_op.argtypes = [vp, vp, ci, ci]
+    H.ref_polys_switch_format.restype = ctypes.c_double
+    H.ref_polys_switch_format.argtypes = [vp, ci]
+    H.ref_polys_set_pim.argtypes = [vp, ci]
+    H.ref_polys_format.argtypes = [vp]
+    H.ref_last_error.restype = ctypes.c_char_p
+    return H
+
+
+def p(a):
+    return a.ctypes.data_as(vp)
+
+
+def run_ops(H, oracle, n, towers, batch, pim_on):
+    q, psi = oracle.gen_params(60, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    a = oracle.fill_ring(batch, n, q, 31)
+    b = oracle.fill_ring(batch, n, q, 32)
+    ctx = H.ref_ctx_create(n, towers, p(q), p(psi))
+    res = np.empty_like(a)
+    try:
+        for op in range(3):
+            ha, hb = H.ref_polys_load(ctx, p(a), batch, 0), H.ref_polys_load(ctx, p(b), batch, 0)
+            if pim_on:
+                assert H.ref_polys_set_pim(ha, 1) == 0, H.ref_last_error()
+            assert H.ref_polys_op(ha, hb, op, 1) >= 0, H.ref_last_error()
+            H.ref_polys_store(ha, p(res))
+            assert np.array_equal(res, octx.elementwise(op, a, b)), f"op {op}"
+            H.ref_polys_free(ha); H.ref_polys_free(hb)
+        ha = H.ref_polys_load(ctx, p(a), batch, 1)                 # COEFFICIENT
+        if pim_on:
+            assert H.ref_polys_set_pim(ha, 1) == 0, H.ref_last_error()
+        assert H.ref_polys_switch_format(ha, 1) >= 0, H.ref_last_error()
+        assert H.ref_polys_format(ha) == 0                         # now EVALUATION
+        H.ref_polys_store(ha, p(res))
+        assert np.array_equal(res, octx.ntt(a, inverse=False))
+        assert H.ref_polys_switch_format(ha, 1) >= 0, H.ref_last_error()
+        assert H.ref_polys_format(ha) == 1
+        H.ref_polys_store(ha, p(res))
+        assert np.array_equal(res, a)
+        # a transform on the GPU followed by a multiply on the CPU path (handle detached): formats stay coherent
+        if pim_on:
+            H.ref_polys_switch_format(ha, 1)
+            assert H.ref_polys_set_pim(ha, 0) == 0
+            hb = H.ref_polys_load(ctx, p(b), batch, 0)
+            assert H.ref_polys_op(ha, hb, 2, 1) >= 0
+            H.ref_polys_store(ha, p(res))
+            assert np.array_equal(res, octx.elementwise(2, octx.ntt(a, inverse=False), b))
+            H.ref_polys_free(hb)
+        H.ref_polys_free(ha)
+    finally:
+        H.ref_ctx_destroy(ctx)
+
+
+def test_hooked_build_without_handle_is_the_cpu_path(hooked, oracle):
+    run_ops(hooked, oracle, 1 << 10, 2, 2, pim_on=False)
+
+
+def test_hooked_build_fails_loudly_without_gpu(hooked, oracle):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    q, psi = oracle.gen_params(60, 1 << 10, 2)
+    a = oracle.fill_ring(1, 1 << 10, q, 1)
+    ctx = hooked.ref_ctx_create(1 << 10, 2, p(q), p(psi))
+    ha = hooked.ref_polys_load(ctx, p(a), 1, 0)
+    assert hooked.ref_polys_set_pim(ha, 1) == 1
+    assert b"no CPU fallback" in hooked.ref_last_error()
+    hooked.ref_polys_free(ha)
+    hooked.ref_ctx_destroy(ctx)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,towers,batch", [(1 << 14, 2, 2), (1 << 12, 5, 1), (1 << 16, 3, 1), (8, 2, 1)])
+def test_live_intercept_matches_cpu_path(hooked, oracle, pkg, n, towers, batch):
+    before = pkg._native.lib.fhe_launch_count()
+    run_ops(hooked, oracle, n, towers, batch, pim_on=True)
+    assert pkg._native.lib.fhe_launch_count() > before, "the intercept did not launch any kernel"
