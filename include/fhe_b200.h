@@ -181,6 +181,10 @@ int fhe_dcrt_op_host(fhe_ring* ring, int op, uint64_t* dst, const uint64_t* a, c
  * constructor, results fetched by sync(), pim/PimData.h:16-34) applied to a whole batch. Blocking. */
 int fhe_dcrt_multi_op_host(fhe_ring* ring, const int* ops, int nops, uint64_t* const* dsts,
                            const uint64_t* a, const uint64_t* b, size_t batch);
+/* The reference's in-place operator sequence on host operands (DCRTPolyImpl::operator+= / -= / *=,
+ * dcrtpoly-impl.h:398-416, dcrtpoly.h:142-148): for i < nops <= 8, a (ops[i])= b, whole batch, the
+ * intermediate values never leave the device; one upload of a and b, one download of a. Blocking. */
+int fhe_dcrt_chain_host(fhe_ring* ring, const int* ops, int nops, uint64_t* a, const uint64_t* b, size_t batch);
 /* in-place transform of a host buffer (inverse = 0 forward, 1 inverse). Blocking. */
 int fhe_ntt_host(fhe_ring* ring, uint64_t* x, size_t batch, int inverse);
 

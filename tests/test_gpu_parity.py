@@ -244,6 +244,11 @@ def test_host_pipeline_vs_oracle(pkg, backend, oracle):
     assert np.array_equal(x, octx.ntt(a, inverse=False))
     ring.ntt_host(x, batch, inverse=True)
     assert np.array_equal(x, a)
+    # the reference's in-place sequence a += b; a *= b; a -= b (dcrtpoly-impl.h:398-416) on host operands
+    x = a.copy()
+    ring.chain_host([ADD, MUL, SUB], x, b, batch)
+    want = octx.elementwise(SUB, octx.elementwise(MUL, octx.elementwise(ADD, a, b), b), b)
+    assert np.array_equal(x, want)
     ring.close()
 
 

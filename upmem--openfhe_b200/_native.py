@@ -59,6 +59,7 @@ SIGNATURES = {
     "fhe_launch": (ci, [vp, ci, vp, u64]),
     "fhe_dcrt_op_host": (ci, [vp, ci, vp, vp, vp, sz]),
     "fhe_dcrt_multi_op_host": (ci, [vp, ctypes.POINTER(ci), ci, ctypes.POINTER(vp), vp, vp, sz]),
+    "fhe_dcrt_chain_host": (ci, [vp, ctypes.POINTER(ci), ci, vp, vp, sz]),
     "fhe_ntt_host": (ci, [vp, vp, sz, ci]),
     "fhe_imad_probe": (ci, [vp, ci, ci, ci, ctypes.POINTER(ctypes.c_float)]),
 }

@@ -792,6 +792,33 @@ extern "C" int fhe_dcrt_multi_op_host(fhe_ring* r, const int* ops, int nops, uin
     return FHE_OK;
 }
 
+extern "C" int fhe_dcrt_chain_host(fhe_ring* r, const int* ops, int nops, uint64_t* a, const uint64_t* b, size_t batch) {
+    if (!r) return fail(FHE_EINVAL, "null ring");
+    if (!ops || nops < 1 || nops > 8) return fail(FHE_EINVAL, "fhe_dcrt_chain_host: need 1..8 ops");
+    for (int i = 0; i < nops; i++)
+        if (ops[i] < FHE_OP_ADD || ops[i] > FHE_OP_MUL) return fail(FHE_EINVAL, "fhe_dcrt_chain_host: unknown op %d", ops[i]);
+    if (batch == 0) return FHE_OK;
+    if (!a || !b) return fail(FHE_EINVAL, "fhe_dcrt_chain_host: null host pointer");
+    CUDA_TRY(cudaSetDevice(r->ctx->device));
+    HostPipe hp(r, true);
+    int rc = hp.reserve(batch, true);
+    if (rc) return rc;
+    size_t k = 0;
+    for (size_t b0 = 0; b0 < batch; b0 += hp.chunk_items, k++) {
+        size_t items = std::min(hp.chunk_items, batch - b0), words = items * hp.item_words;
+        size_t slot = k % hp.nslots;
+        cudaStream_t s = r->ctx->streams[slot];
+        uint64_t* da = (uint64_t*)hp.bufA[slot];
+        uint64_t* db = (uint64_t*)hp.bufB[slot];
+        CUDA_TRY(cudaMemcpyAsync(da, a + b0 * hp.item_words, words * 8, cudaMemcpyHostToDevice, s));
+        CUDA_TRY(cudaMemcpyAsync(db, b + b0 * hp.item_words, words * 8, cudaMemcpyHostToDevice, s));
+        for (int i = 0; i < nops; i++) CUDA_TRY(launch_elementwise(r->dev, ops[i], da, da, db, items, s));
+        CUDA_TRY(cudaMemcpyAsync(a + b0 * hp.item_words, da, words * 8, cudaMemcpyDeviceToHost, s));
+    }
+    for (size_t i = 0; i < hp.nslots; i++) CUDA_TRY(cudaStreamSynchronize(r->ctx->streams[i]));
+    return FHE_OK;
+}
+
 extern "C" int fhe_dcrt_op_host(fhe_ring* r, int op, uint64_t* dst, const uint64_t* a, const uint64_t* b, size_t batch) {
     uint64_t* d[1] = {dst};
     return fhe_dcrt_multi_op_host(r, &op, 1, d, a, b, batch);

@@ -175,6 +175,12 @@ class Ring:
         c_dsts = (ctypes.c_void_p * n)(*[d.ctypes.data for d in dsts])
         N.check(N.lib.fhe_dcrt_multi_op_host(self.h, c_ops, n, c_dsts, _ptr(a), _ptr(b), batch))
 
+    def chain_host(self, ops, a, b, batch):
+        """a (ops[i])= b in sequence, in place on the host buffer `a` (the reference's += / -= / *=);
+        one upload of a and b, one download of a."""
+        n = len(ops)
+        N.check(N.lib.fhe_dcrt_chain_host(self.h, (ctypes.c_int * n)(*ops), n, _ptr(a), _ptr(b), batch))
+
     def ntt_host(self, x, batch, inverse=False):
         N.check(N.lib.fhe_ntt_host(self.h, _ptr(x), batch, 1 if inverse else 0))
 
