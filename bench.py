@@ -376,6 +376,26 @@ def ntt_extra(pkg, be):
             for b_ in bufs:
                 be.free(b_)
             ring.close()
+        # automorphism (rotation) in both formats: 16 B of HBM traffic per coefficient
+        n, towers, batch = 1 << 16, 30, 64
+        q, psi = pkg.gen_params(60, n, towers)
+        ring = pkg.Ring(be, n, q, psi)
+        words = ring.words(batch)
+        src, dst = be.alloc(words * 8), be.alloc(words * 8)
+        ring.fill_uniform(src, batch, 20260020)
+        lib = pkg._native.lib
+        for fmt, name in ((0, "automorphism_eval_n65536_t30_b64"), (1, "automorphism_coef_n65536_t30_b64")):
+            for _ in range(2):
+                pkg._native.check(lib.fhe_automorphism(ring.h, dst, src, batch, 5, fmt, 0))
+            be.sync()
+            reps = 10
+            be.timer_start(0)
+            for _ in range(reps):
+                pkg._native.check(lib.fhe_automorphism(ring.h, dst, src, batch, 5, fmt, 0))
+            ms = be.timer_stop(0) / reps
+            out[name] = {"ms": ms, "coeff_per_s": words / (ms * 1e-3), "hbm_gbs": 16 * words / (ms * 1e-3) / 1e9}
+        be.free(src); be.free(dst)
+        ring.close()
     except Exception as ex:
         out["error"] = str(ex)[:300]
     return out

@@ -26,6 +26,8 @@
  *     math/hal/intnat/transformnat-impl.h:575-602,637-666
  *   ChineseRemainderTransformFTTNat::PreCompute (twiddle cache)  fhe_ring_create
  *     transformnat-impl.h:708-763
+ *   DCRTPolyImpl::AutomorphismTransform (k) / (k, precomp)       fhe_automorphism / fhe_automorphism_map
+ *     dcrtpoly-impl.h:348-369, poly-impl.h:312-380
  *   FirstPrime / PreviousPrime / RootOfUnity parameter recipe    fhe_gen_params (host side, setup only)
  *     math/nbtheory-impl.h:183-231,334-379;
  *     benchmark/src/poly-benchmark-16k.cpp:82-101
@@ -144,6 +146,16 @@ int fhe_ct_tensor_product(fhe_ring* ring, const fhe_dptr* c, const fhe_dptr* a, 
  * inputs, tensor product, forward NTT of the outputs (config 4's wording). */
 int fhe_ct_multiply(fhe_ring* ring, const fhe_dptr* c, const fhe_dptr* a, const fhe_dptr* b, size_t batch,
                     int transform, int stream);
+/* Ring automorphism X -> X^k, k odd (DCRTPolyImpl::AutomorphismTransform, dcrtpoly-impl.h:348-369 ->
+ * PolyImpl::AutomorphismTransform, poly-impl.h:312-365), every tower of every polynomial of the batch, one
+ * launch.  format 0 = EVALUATION (bit-reversed order; index map computed on the fly), 1 = COEFFICIENT
+ * (a negated zero is stored as q, as the reference's `q - value` does).  k even -> FHE_EINVAL
+ * ("Automorphism index not odd", the reference's math_error).  dst must not be src. */
+int fhe_automorphism(fhe_ring* ring, fhe_dptr dst, fhe_dptr src, size_t batch, uint32_t k, int format, int stream);
+/* PrecomputeAutoMap (src/core/lib/math/nbtheory2.cpp:274-286): map[rev(j)] = rev(((2j+1)k mod 2N) >> 1); host. */
+int fhe_precompute_automap(uint32_t N, uint32_t k, uint32_t* map);
+/* The two-argument form (poly-impl.h:368-380): dst[j] = src[map[j]] per tower, map = N uint32 in HBM. */
+int fhe_automorphism_map(fhe_ring* ring, fhe_dptr dst, fhe_dptr src, size_t batch, fhe_dptr map, int stream);
 /* seeded uniform coefficients in [0, q_tower) (synthetic inputs for tests and benchmarks) */
 int fhe_fill_uniform(fhe_ring* ring, fhe_dptr dst, size_t batch, uint64_t seed, int stream);
 

@@ -10,6 +10,7 @@
  *   Plus / Minus / Times            lattice/hal/default/dcrtpoly.h:164-200, dcrtpoly-impl.h:398-407
  *   operator+= -= *= (no checks)    dcrtpoly-impl.h:410-416, 438-444, dcrtpoly.h:142-148
  *   SwitchFormat / SetFormat        dcrtpoly-impl.h:2518-2524, lattice/ilelement.h:448-451
+ *   AutomorphismTransform           dcrtpoly-impl.h:348-369, poly-impl.h:312-380
  * Layout in HBM: [batch][tower][N] uint64.  Header only; link with libfhe_b200.so.
  */
 #ifndef _PIM_DCRT_POLY_
@@ -117,6 +118,22 @@ public:
       PimManager::check(fhe_ntt_inverse(ring_->handle(), d_, batch_, stream_), "SwitchFormat");
       format_ = PIM_COEFFICIENT;
     }
+  }
+  /* dcrtpoly-impl.h:348-358 -> poly-impl.h:312-365; k even throws math_error there */
+  PimDCRTPoly AutomorphismTransform(uint32_t k) const {
+    if (k % 2 == 0) throw pim_math_error("Automorphism index not odd\n");
+    PimDCRTPoly out(ring_, batch_, format_, nullptr, stream_);
+    PimManager::check(fhe_automorphism(ring_->handle(), out.d_, d_, batch_, k, (int)format_, stream_), "AutomorphismTransform");
+    return out;
+  }
+  /* dcrtpoly-impl.h:360-369 -> poly-impl.h:368-380; `precomp` = device copy of PrecomputeAutoMap's table */
+  PimDCRTPoly AutomorphismTransform(uint32_t k, fhe_dptr precomp) const {
+    if (format_ != PIM_EVALUATION)
+      throw pim_not_implemented_error("Automorphism Poly Format not EVALUATION or not power-of-two");
+    if (k % 2 == 0) throw pim_math_error("Automorphism index not odd\n");
+    PimDCRTPoly out(ring_, batch_, format_, nullptr, stream_);
+    PimManager::check(fhe_automorphism_map(ring_->handle(), out.d_, d_, batch_, precomp, stream_), "AutomorphismTransform");
+    return out;
   }
   void SetFormat(PimFormat f) { if (format_ != f) SwitchFormat(); }
 

@@ -401,6 +401,51 @@ void orc_ctx_destroy(orc_ctx* c) {
     free(c);
 }
 
+/* ---- automorphism ---- */
+static uint32_t ilog2_u32(uint32_t n) { uint32_t l = 0; while ((1u << l) < n) l++; return l; }
+
+/* poly-impl.h:312-365: EVALUATION: result[rev(j)] = in[rev(((2j+1)k >> 1) & mask)];
+ * COEFFICIENT: result[jk & mask] = bit logn of jk set ? q - in[j] : in[j]  (32-bit wrapping jk). */
+int orc_automorphism(uint64_t* out, const uint64_t* in, uint32_t N, uint64_t q, uint32_t k, int format) {
+    if (k % 2 == 0) return 1;                                    /* "Automorphism index not odd" */
+    uint32_t logn = ilog2_u32(N), mask = (uint32_t)((1ull << logn) - 1);
+    if (format == 0) {
+        uint32_t jk = k;
+        for (uint32_t j = 0; j < N; j++, jk += 2 * k)
+            out[bitrev(j, logn)] = in[bitrev((jk >> 1) & mask, logn)];
+    } else {
+        uint32_t jk = 0;
+        for (uint32_t j = 0; j < N; j++, jk += k)
+            out[jk & mask] = ((jk >> logn) & 1) ? q - in[j] : in[j];
+    }
+    return 0;
+}
+
+/* nbtheory2.cpp:274-286 */
+void orc_precompute_automap(uint32_t N, uint32_t k, uint32_t* map) {
+    uint32_t logn = ilog2_u32(N), logm = logn + 1;
+    for (uint32_t j = 0; j < N; j++) {
+        uint32_t jt = (j << 1) + 1;
+        uint32_t idx = ((jt * k) - (((jt * k) >> logm) << logm)) >> 1;
+        map[bitrev(j, logn)] = bitrev(idx, logn);
+    }
+}
+
+/* poly-impl.h:368-380 */
+void orc_automorphism_map(uint64_t* out, const uint64_t* in, uint32_t N, const uint32_t* map) {
+    for (uint32_t j = 0; j < N; j++) out[j] = in[map[j]];
+}
+
+/* dcrtpoly-impl.h:348-369: tower by tower */
+int orc_dcrt_automorphism(const orc_ctx* c, uint64_t* out, const uint64_t* in, size_t B, uint32_t k, int format) {
+    if (k % 2 == 0) return 1;
+    long units = (long)(B * c->T);
+#pragma omp parallel for schedule(static)
+    for (long u = 0; u < units; u++)
+        orc_automorphism(out + (size_t)u * c->N, in + (size_t)u * c->N, c->N, c->q[u % c->T], k, format);
+    return 0;
+}
+
 int orc_max_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

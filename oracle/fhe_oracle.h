@@ -79,6 +79,17 @@ void     orc_dcrt_elementwise(const orc_ctx* c, int op, uint64_t* dst, const uin
 void     orc_dcrt_ntt(const orc_ctx* c, int inverse, uint64_t* x, size_t B, int nthreads);
 int      orc_max_threads(void);
 
+/* ---- automorphism X -> X^k, k odd ----
+ * orc_automorphism: one tower, PolyImpl::AutomorphismTransform(k) (poly-impl.h:312-365); format 0 =
+ * EVALUATION (bit-reversed order), 1 = COEFFICIENT (a negated zero is stored as q, as the reference's
+ * `q - value` does).  orc_precompute_automap: PrecomputeAutoMap (nbtheory2.cpp:274-286);
+ * orc_automorphism_map: the two-argument form (poly-impl.h:368-380).  The dcrt form applies it to
+ * [B][T][N].  Return 1 where the reference throws (k even). */
+int  orc_automorphism(uint64_t* out, const uint64_t* in, uint32_t N, uint64_t q, uint32_t k, int format);
+void orc_precompute_automap(uint32_t N, uint32_t k, uint32_t* map);
+void orc_automorphism_map(uint64_t* out, const uint64_t* in, uint32_t N, const uint32_t* map);
+int  orc_dcrt_automorphism(const orc_ctx* c, uint64_t* out, const uint64_t* in, size_t B, uint32_t k, int format);
+
 /* ---- seeded input generator shared with the product's device-side fill
  * (counter based: value i depends only on (seed, i, q)) ---- */
 uint64_t orc_uniform_at(uint64_t seed, uint64_t i, uint64_t q);

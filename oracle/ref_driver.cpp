@@ -186,6 +186,30 @@ ref_polys* ref_polys_binary(const ref_polys* a, const ref_polys* b, int op) {
     return r;
 }
 
+// DCRTPoly::AutomorphismTransform (dcrtpoly-impl.h:348-369 -> poly-impl.h:312-380) on every poly of the batch.
+// precomp != 0: the two-argument form with the table of PrecomputeAutoMap (nbtheory2.cpp:274-286), which is what
+// the schemes call (EVALUATION only).  Returns a new batch, or NULL if the reference threw.
+ref_polys* ref_polys_automorphism(const ref_polys* a, uint32_t k, int precomp) {
+    auto* r = new ref_polys{a->ctx, {}};
+    try {
+        std::vector<uint32_t> map(a->ctx->N);
+        if (precomp) PrecomputeAutoMap(a->ctx->N, k, &map);
+        for (size_t i = 0; i < a->v.size(); i++)
+            r->v.push_back(precomp ? a->v[i].AutomorphismTransform(k, map) : a->v[i].AutomorphismTransform(k));
+        return r;
+    }
+    catch (const std::exception& e) {
+        g_ref_err = e.what();
+        delete r;
+        return nullptr;
+    }
+}
+void ref_precompute_automap(uint32_t n, uint32_t k, uint32_t* out) {
+    std::vector<uint32_t> map(n);
+    PrecomputeAutoMap(n, k, &map);
+    std::memcpy(out, map.data(), n * sizeof(uint32_t));
+}
+
 // mod-ops of the PimData surface executed by the reference's own NativeVector (in-place forms:
 // mubintvecnat.cpp:111-195,370-487, mubintvecnat.h:560-566).  kind = enum mod_kernel.
 // Returns 0, or 1 if the reference threw.

@@ -40,6 +40,10 @@ class Oracle:
             ("orc_dcrt_elementwise", None, [vp, ci, vp, vp, vp, sz, ci]),
             ("orc_dcrt_ntt", None, [vp, ci, vp, sz, ci]), ("orc_max_threads", ci, []),
             ("orc_vec_modop", ci, [ci, vp, vp, sz, u64, u64, u64]),
+            ("orc_automorphism", ci, [vp, vp, u32, u64, u32, ci]),
+            ("orc_precompute_automap", None, [u32, u32, vp]),
+            ("orc_automorphism_map", None, [vp, vp, u32, vp]),
+            ("orc_dcrt_automorphism", ci, [vp, vp, vp, sz, u32, ci]),
             ("orc_uniform_at", u64, [u64, u64, u64]), ("orc_fill_uniform", None, [vp, sz, u64, u64, u64]),
         ]:
             f = getattr(L, name)
@@ -133,6 +137,26 @@ class OracleCtx:
         batch = x.size // (len(self.q) * self.n)
         self.o.L.orc_dcrt_ntt(self.h, 1 if inverse else 0, _p(x), batch, threads)
         return x
+
+
+def _automorphism(self, x, k, fmt=0):
+    """DCRTPolyImpl::AutomorphismTransform(k) over [B][T][N]; fmt 0 EVALUATION, 1 COEFFICIENT."""
+    x = np.ascontiguousarray(x, np.uint64)
+    out = np.empty_like(x)
+    batch = x.size // (len(self.q) * self.n)
+    if self.o.L.orc_dcrt_automorphism(self.h, _p(out), _p(x), batch, k, fmt):
+        raise ValueError("Automorphism index not odd")
+    return out
+
+
+def _automap(self, n, k):
+    m = np.empty(n, np.uint32)
+    self.L.orc_precompute_automap(n, k, _p(m))
+    return m
+
+
+OracleCtx.automorphism = _automorphism
+Oracle.automap = _automap
 
 
 def load():

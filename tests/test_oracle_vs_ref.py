@@ -30,6 +30,10 @@ def ref():
     R.ref_polys_op.argtypes = [vp, vp, ci, ci]
     R.ref_polys_switch_format.restype = ctypes.c_double
     R.ref_polys_switch_format.argtypes = [vp, ci]
+    R.ref_polys_automorphism.restype = vp
+    R.ref_polys_automorphism.argtypes = [vp, u32, ci]
+    R.ref_precompute_automap.argtypes = [u32, u32, vp]
+    R.ref_last_error.restype = ctypes.c_char_p
     return R
 
 
@@ -73,4 +77,39 @@ def test_params_and_ops_match_reference(oracle, ref, nbits, n, towers):
     ref.ref_polys_store(hb, p(res))
     assert np.array_equal(res, octx.ntt(b, inverse=True))
     ref.ref_polys_free(hb)
+    ref.ref_ctx_destroy(ctx)
+
+
+@pytest.mark.parametrize("n,towers", [(8, 2), (1 << 10, 3), (1 << 14, 2)])
+def test_automorphism_matches_reference(oracle, ref, n, towers):
+    """SURVEY §8(f) rank 4: DCRTPoly::AutomorphismTransform(k) and (k, precomp), both formats."""
+    q, psi = oracle.gen_params(60, n, towers)
+    rng = np.random.default_rng(n)
+    batch = 2
+    a = np.stack([rng.integers(0, int(m), size=(batch, n), dtype=np.uint64) for m in q], axis=1)
+    a[0, :, :3] = 0                                     # negated zeros: the reference stores q
+    octx = oracle.ctx(n, q, psi)
+    ctx = ref.ref_ctx_create(n, towers, p(q), p(psi))
+    res = np.empty_like(a)
+    for k in (3, 5, 2 * n - 1, n + 1, 25 % (2 * n) | 1):
+        mr = np.empty(n, np.uint32)
+        ref.ref_precompute_automap(n, k, p(mr))
+        assert np.array_equal(mr, oracle.automap(n, k))
+        for fmt in (0, 1):
+            ha = ref.ref_polys_load(ctx, p(a), batch, fmt)
+            hr = ref.ref_polys_automorphism(ha, k, 0)
+            assert hr, ref.ref_last_error()
+            ref.ref_polys_store(hr, p(res))
+            assert np.array_equal(res, octx.automorphism(a, k, fmt)), (k, fmt)
+            ref.ref_polys_free(hr)
+            if fmt == 0:
+                hr = ref.ref_polys_automorphism(ha, k, 1)
+                assert hr, ref.ref_last_error()
+                ref.ref_polys_store(hr, p(res))
+                assert np.array_equal(res, octx.automorphism(a, k, 0)), (k, "precomp")
+                ref.ref_polys_free(hr)
+            ref.ref_polys_free(ha)
+    ha = ref.ref_polys_load(ctx, p(a), batch, 0)
+    assert not ref.ref_polys_automorphism(ha, 4, 0) and b"not odd" in ref.ref_last_error()
+    ref.ref_polys_free(ha)
     ref.ref_ctx_destroy(ctx)

@@ -51,6 +51,9 @@ SIGNATURES = {
     "fhe_poly_mul": (ci, [vp, u64, u64, u64, sz, ci]),
     "fhe_ct_tensor_product": (ci, [vp, pu64, pu64, pu64, sz, ci]),
     "fhe_ct_multiply": (ci, [vp, pu64, pu64, pu64, sz, ci, ci]),
+    "fhe_automorphism": (ci, [vp, u64, u64, sz, u32, ci, ci]),
+    "fhe_precompute_automap": (ci, [u32, u32, vp]),
+    "fhe_automorphism_map": (ci, [vp, u64, u64, sz, u64, ci]),
     "fhe_fill_uniform": (ci, [vp, u64, sz, u64, ci]),
     "fhe_vec_op": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),
     "fhe_vec_op_scalar": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),

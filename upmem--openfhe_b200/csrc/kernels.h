@@ -37,6 +37,12 @@ cudaError_t launch_vec_scalar(int op, uint64_t* dst, const uint64_t* a, uint64_t
 // algo: 0 = auto, 1 = force the single-CTA shared-memory kernel (N <= 4096).
 cudaError_t launch_ntt(const RingDev& r, uint64_t* data, size_t batch, bool inverse,
                        cudaStream_t st, int algo);
+// dst = automorphism X -> X^k of src over [batch][T][N] (k odd, dst != src).  format 0 EVALUATION, 1 COEFFICIENT.
+cudaError_t launch_automorphism(const RingDev& r, uint64_t* dst, const uint64_t* src, size_t batch, uint32_t k,
+                                int format, cudaStream_t st);
+// dst[j] = src[map[j]] per tower (map: N uint32 in HBM), the precomputed-table form.
+cudaError_t launch_automorphism_map(const RingDev& r, uint64_t* dst, const uint64_t* src, size_t batch,
+                                    const uint32_t* map, cudaStream_t st);
 // Counter-based uniform fill in [0, q_t) per tower (same definition as the test oracle's generator).
 cudaError_t launch_fill_uniform(const RingDev& r, uint64_t* dst, size_t batch, uint64_t seed,
                                 cudaStream_t st);

@@ -537,6 +537,44 @@ extern "C" int fhe_poly_mul(fhe_ring* r, fhe_dptr c, fhe_dptr a, fhe_dptr b, siz
     return fhe_ntt_inverse(r, c, batch, stream);
 }
 
+extern "C" int fhe_automorphism(fhe_ring* r, fhe_dptr dst, fhe_dptr src, size_t batch, uint32_t k, int format, int stream) {
+    cudaStream_t s;
+    int rc = ring_stream(r, stream, &s);
+    if (rc) return rc;
+    if (format != 0 && format != 1) return fail(FHE_EINVAL, "fhe_automorphism: format must be 0 (EVALUATION) or 1 (COEFFICIENT)");
+    if (k % 2 == 0) return fail(FHE_EINVAL, "Automorphism index not odd");          // poly-impl.h:346-347
+    if (batch == 0) return FHE_OK;
+    if (!dst || !src) return fail(FHE_EINVAL, "fhe_automorphism: null device pointer");
+    if (dst == src) return fail(FHE_EINVAL, "fhe_automorphism: dst must not alias src (it is a permutation)");
+    CUDA_TRY(launch_automorphism(r->dev, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, batch, k, format, s));
+    return FHE_OK;
+}
+
+extern "C" int fhe_precompute_automap(uint32_t N, uint32_t k, uint32_t* map) {
+    if (!map) return fail(FHE_EINVAL, "fhe_precompute_automap: null output");
+    if (N == 0 || (N & (N - 1))) return fail(FHE_EINVAL, "fhe_precompute_automap: N must be a power of two");
+    uint32_t logn = 0;
+    while ((1u << logn) < N) logn++;
+    auto rev = [logn](uint32_t x) { uint32_t r = 0; for (uint32_t i = 0; i < logn; i++) { r = (r << 1) | (x & 1); x >>= 1; } return r; };
+    for (uint32_t j = 0; j < N; j++) {
+        uint32_t idx = (((2 * j + 1) * k) & (2 * N - 1)) >> 1;
+        map[rev(j)] = rev(idx);
+    }
+    return FHE_OK;
+}
+
+extern "C" int fhe_automorphism_map(fhe_ring* r, fhe_dptr dst, fhe_dptr src, size_t batch, fhe_dptr map, int stream) {
+    cudaStream_t s;
+    int rc = ring_stream(r, stream, &s);
+    if (rc) return rc;
+    if (batch == 0) return FHE_OK;
+    if (!dst || !src || !map) return fail(FHE_EINVAL, "fhe_automorphism_map: null device pointer");
+    if (dst == src) return fail(FHE_EINVAL, "fhe_automorphism_map: dst must not alias src");
+    CUDA_TRY(launch_automorphism_map(r->dev, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, batch,
+                                     (const uint32_t*)(uintptr_t)map, s));
+    return FHE_OK;
+}
+
 extern "C" int fhe_ct_tensor_product(fhe_ring* r, const fhe_dptr* c, const fhe_dptr* a, const fhe_dptr* b,
                                      size_t batch, int stream) {
     cudaStream_t s;

@@ -261,6 +261,20 @@ class DCRTPolyBatch:
     def __imul__(self, rhs):
         return self._inplace(rhs, N.OP_MUL)
 
+    def AutomorphismTransform(self, k, precomp=None):
+        """dcrtpoly-impl.h:348-369.  precomp: device address of the PrecomputeAutoMap table (EVALUATION only,
+        poly-impl.h:368-380); without it the index map is computed in the kernel."""
+        if k % 2 == 0:
+            raise RuntimeError("Automorphism index not odd")
+        out = DCRTPolyBatch(self.ring, self.batch, self.format, stream=self.stream)
+        if precomp is not None:
+            if self.format != EVALUATION:
+                raise RuntimeError("Automorphism Poly Format not EVALUATION or not power-of-two")
+            N.check(N.lib.fhe_automorphism_map(self.ring.h, out.dptr, self.dptr, self.batch, precomp, self.stream))
+        else:
+            N.check(N.lib.fhe_automorphism(self.ring.h, out.dptr, self.dptr, self.batch, k, self.format, self.stream))
+        return out
+
     def SwitchFormat(self):
         """dcrtpoly-impl.h:2518-2524: COEFFICIENT -> forward NTT, EVALUATION -> inverse."""
         if self.format == COEFFICIENT:
