@@ -446,6 +446,200 @@ int orc_dcrt_automorphism(const orc_ctx* c, uint64_t* out, const uint64_t* in, s
     return 0;
 }
 
+/* ---- RNS basis conversion and scaling ---- */
+static uint64_t mulmod_u128(uint64_t a, uint64_t b, uint64_t m) { return (uint64_t)(((u128)a * b) % m); }
+
+void orc_switch_tables(const uint64_t* q, uint32_t sq, const uint64_t* p, uint32_t sp, uint64_t* hat_inv, uint64_t* hat_modp) {
+    for (uint32_t i = 0; i < sq; i++) {
+        uint64_t h = 1 % q[i];
+        for (uint32_t k = 0; k < sq; k++) if (k != i) h = mulmod_u128(h, q[k] % q[i], q[i]);
+        hat_inv[i] = orc_modinv(h, q[i]);
+        for (uint32_t j = 0; j < sp; j++) {
+            uint64_t g = 1 % p[j];
+            for (uint32_t k = 0; k < sq; k++) if (k != i) g = mulmod_u128(g, q[k] % p[j], p[j]);
+            hat_modp[(size_t)i * sp + j] = g;
+        }
+    }
+}
+
+/* Ql * [Ql^-1]_ql = 1 + m*ql, so floor(.../ql) = m, and m = -ql^-1 (mod q_i) because q_i divides Ql. */
+void orc_rescale_tables(const uint64_t* q, uint32_t T, uint64_t* qlql, uint64_t* qlinv) {
+    uint32_t l = T - 1;
+    for (uint32_t i = 0; i < l; i++) {
+        qlinv[i] = orc_modinv(q[l] % q[i], q[i]);
+        qlql[i] = (q[i] - qlinv[i]) % q[i];
+    }
+}
+
+static int add_carry_out(uint64_t a, uint64_t b, uint64_t* c) { *c = a + b; return *c < a; }
+
+/* utils/utilities-int.h:60-110, statement by statement */
+static uint64_t barrett128(u128 a, uint64_t modulus, u128 mu) {
+    uint64_t a_lo = (uint64_t)a, a_hi = (uint64_t)(a >> 64), mu_lo = (uint64_t)mu, mu_hi = (uint64_t)(mu >> 64);
+    uint64_t left_hi = (uint64_t)(((u128)a_lo * mu_lo) >> 64);
+    u128 middle = (u128)a_lo * mu_hi;
+    uint64_t middle_lo = (uint64_t)middle, middle_hi = (uint64_t)(middle >> 64), tmp1, tmp2;
+    uint64_t carry = (uint64_t)add_carry_out(middle_lo, left_hi, &tmp1);
+    tmp2 = middle_hi + carry;
+    middle = (u128)a_hi * mu_lo;
+    middle_lo = (uint64_t)middle; middle_hi = (uint64_t)(middle >> 64);
+    carry = (uint64_t)((uint64_t)(middle_lo + tmp1) < middle_lo);           /* IsAdditionOverflow */
+    left_hi = middle_hi + carry;
+    tmp1 = a_hi * mu_hi + tmp2 + left_hi;
+    uint64_t result = a_lo - tmp1 * modulus;
+    while (result >= modulus) result -= modulus;
+    return result;
+}
+
+void orc_approx_switch(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, const uint64_t* q, uint32_t sq,
+                       const uint64_t* p, uint32_t sp, const uint64_t* hat_inv, const uint64_t* hat_modp) {
+    uint64_t* pre = (uint64_t*)malloc(sizeof(uint64_t) * sq);
+    u128* mu = (u128*)malloc(sizeof(u128) * sp);
+    for (uint32_t i = 0; i < sq; i++) pre[i] = orc_prep_mulconst(hat_inv[i], q[i]);
+    for (uint32_t j = 0; j < sp; j++) mu[j] = (~(u128)0) / p[j];     /* floor(2^128 / p_j): p_j is not a power of two */
+    long items = (long)(B * N);
+#pragma omp parallel for schedule(static)
+    for (long e = 0; e < items; e++) {
+        size_t b = (size_t)e / N, ri = (size_t)e % N;
+        u128 sum[64];
+        for (uint32_t j0 = 0; j0 < sp; j0 += 64) {
+            uint32_t jn = sp - j0 < 64 ? sp - j0 : 64;
+            for (uint32_t j = 0; j < jn; j++) sum[j] = 0;
+            for (uint32_t i = 0; i < sq; i++) {
+                uint64_t xi = in[(b * sq + i) * N + ri];
+                uint64_t y = orc_modmul_const(xi, hat_inv[i], q[i], pre[i]);
+                for (uint32_t j = 0; j < jn; j++) sum[j] += (u128)y * hat_modp[(size_t)i * sp + j0 + j];
+            }
+            for (uint32_t j = 0; j < jn; j++) out[(b * sp + j0 + j) * N + ri] = barrett128(sum[j], p[j0 + j], mu[j0 + j]);
+        }
+    }
+    free(pre); free(mu);
+}
+
+/* gather / scatter of a tower range between [B][Tsrc][N] and [B][cnt][N] */
+static void towers_copy(uint64_t* dst, uint32_t Tdst, uint32_t d0, const uint64_t* src, uint32_t Tsrc, uint32_t s0,
+                        uint32_t cnt, size_t B, uint32_t N) {
+    for (size_t b = 0; b < B; b++)
+        memcpy(dst + (b * Tdst + d0) * N, src + (b * Tsrc + s0) * N, (size_t)cnt * N * 8);
+}
+/* NativeVectorT::SwitchModulus on one value (mubintvecnat.cpp:112-135) */
+static uint64_t switch_modulus1(uint64_t v, uint64_t om, uint64_t nm) {
+    uint64_t half = om >> 1;
+    if (nm > om) { if (v > half) v += nm - om; return v; }
+    if (v > half) v += nm - (om % nm);
+    if (v >= nm) v %= nm;
+    return v;
+}
+/* NativeVectorT::ModMulEq(scalar) on one value (mubintvecnat.cpp:323-332) */
+static uint64_t mulc1(uint64_t v, uint64_t c, uint64_t q) {
+    static __thread uint64_t kc[2], kq[2], kp[2];          /* PrepModMulConst of the last two (c, q) pairs */
+    static __thread int turn;
+    if (c >= q) c %= q;
+    int s = (kq[0] == q && kc[0] == c) ? 0 : (kq[1] == q && kc[1] == c) ? 1 : -1;
+    if (s < 0) { s = turn; turn ^= 1; kc[s] = c; kq[s] = q; kp[s] = orc_prep_mulconst(c, q); }
+    return orc_modmul_const(v, c, q, kp[s]);
+}
+
+void orc_approx_mod_up(const orc_ctx* Q, const orc_ctx* P, uint64_t* out, const uint64_t* in, size_t B, int format) {
+    uint32_t N = Q->N, sq = Q->T, sp = P->T;
+    size_t wq = B * sq * (size_t)N, wp = B * sp * (size_t)N;
+    uint64_t* coef = (uint64_t*)malloc(wq * 8);
+    uint64_t* partP = (uint64_t*)malloc(wp * 8);
+    uint64_t* hi = (uint64_t*)malloc(sizeof(uint64_t) * sq);
+    uint64_t* hm = (uint64_t*)malloc(sizeof(uint64_t) * sq * sp);
+    memcpy(coef, in, wq * 8);
+    if (format == 0) orc_dcrt_ntt(Q, 1, coef, B, 0);                     /* SetFormat(COEFFICIENT), :1096-1099 */
+    orc_switch_tables(Q->q, sq, P->q, sp, hi, hm);
+    orc_approx_switch(partP, coef, B, N, Q->q, sq, P->q, sp, hi, hm);    /* :1105-1106 */
+    orc_dcrt_ntt(P, 0, partP, B, 0);                                     /* :1113-1116 */
+    towers_copy(out, sq + sp, sq, partP, sp, 0, sp, B, N);
+    if (format == 0) {
+        towers_copy(out, sq + sp, 0, in, sq, 0, sq, B, N);               /* :1119-1123 the stored EVALUATION towers */
+    } else {
+        orc_dcrt_ntt(Q, 0, coef, B, 0);                                  /* :1124-1130 */
+        towers_copy(out, sq + sp, 0, coef, sq, 0, sq, B, N);
+    }
+    free(coef); free(partP); free(hi); free(hm);
+}
+
+void orc_approx_mod_down(const orc_ctx* Q, const orc_ctx* P, uint64_t* out, const uint64_t* in, size_t B, uint64_t t) {
+    uint32_t N = Q->N, sq = Q->T, sp = P->T;
+    size_t wq = B * sq * (size_t)N, wp = B * sp * (size_t)N;
+    uint64_t* partP = (uint64_t*)malloc(wp * 8);
+    uint64_t* sw = (uint64_t*)malloc(wq * 8);
+    uint64_t* hi = (uint64_t*)malloc(sizeof(uint64_t) * sp);
+    uint64_t* hm = (uint64_t*)malloc(sizeof(uint64_t) * sq * sp);
+    towers_copy(partP, sp, 0, in, sq + sp, sq, sp, B, N);                /* :1150-1151 */
+    orc_dcrt_ntt(P, 1, partP, B, 0);
+    if (t)                                                               /* :1152-1154, [t^-1]_{p_j} */
+        for (size_t b = 0; b < B; b++)
+            for (uint32_t j = 0; j < sp; j++) {
+                uint64_t tinv = orc_modinv(t % P->q[j], P->q[j]);
+                uint64_t* v = partP + (b * sp + j) * N;
+                for (uint32_t n = 0; n < N; n++) v[n] = mulc1(v[n], tinv, P->q[j]);
+            }
+    orc_switch_tables(P->q, sp, Q->q, sq, hi, hm);
+    orc_approx_switch(sw, partP, B, N, P->q, sp, Q->q, sq, hi, hm);      /* :1158-1159 */
+    if (t)                                                               /* :1170-1171 */
+        for (size_t b = 0; b < B; b++)
+            for (uint32_t i = 0; i < sq; i++) {
+                uint64_t* v = sw + (b * sq + i) * N;
+                for (uint32_t n = 0; n < N; n++) v[n] = mulc1(v[n], t, Q->q[i]);
+            }
+    orc_dcrt_ntt(Q, 0, sw, B, 0);                                        /* :1172 */
+    for (uint32_t i = 0; i < sq; i++) {                                  /* :1173, [P^-1]_{q_i} */
+        uint64_t qi = Q->q[i], pm = 1 % qi;
+        for (uint32_t j = 0; j < sp; j++) pm = mulmod_u128(pm, P->q[j] % qi, qi);
+        uint64_t pinv = orc_modinv(pm, qi);
+        for (size_t b = 0; b < B; b++) {
+            const uint64_t* x = in + (b * (sq + sp) + i) * N;
+            const uint64_t* s2 = sw + (b * sq + i) * N;
+            uint64_t* o = out + (b * sq + i) * N;
+            for (uint32_t n = 0; n < N; n++) o[n] = mulc1(orc_modsub_fast(x[n], s2[n], qi), pinv, qi);
+        }
+    }
+    free(partP); free(sw); free(hi); free(hm);
+}
+
+void orc_rescale(const orc_ctx* full, const orc_ctx* rest, const orc_ctx* last, uint64_t* out, const uint64_t* in,
+                 size_t B, int format, uint64_t t) {
+    uint32_t N = full->N, T = full->T, l = T - 1;
+    uint64_t ql = full->q[l];
+    uint64_t* lastp = (uint64_t*)malloc(B * (size_t)N * 8);
+    uint64_t* tmp = (uint64_t*)malloc(B * l * (size_t)N * 8);
+    uint64_t* c = (uint64_t*)malloc(sizeof(uint64_t) * l);
+    uint64_t* qlinv = (uint64_t*)malloc(sizeof(uint64_t) * l);
+    orc_rescale_tables(full->q, T, c, qlinv);
+    towers_copy(lastp, 1, 0, in, T, l, 1, B, N);
+    if (format == 0) orc_dcrt_ntt(last, 1, lastp, B, 0);                 /* lastPoly.SetFormat(COEFFICIENT) */
+    if (t) {                                                             /* ModReduce :798: delta *= negtInvModq */
+        uint64_t negtinv = ql - orc_modinv(t % ql, ql);
+        for (size_t k = 0; k < B * (size_t)N; k++) lastp[k] = mulc1(lastp[k], negtinv, ql);
+    }
+    for (size_t b = 0; b < B; b++)
+        for (uint32_t i = 0; i < l; i++) {
+            uint64_t qi = full->q[i];
+            uint64_t* v = tmp + (b * l + i) * N;
+            for (uint32_t n = 0; n < N; n++) {
+                uint64_t x = switch_modulus1(lastp[b * N + n], ql, qi);  /* :757 / :806 */
+                v[n] = t ? x : mulc1(x, c[i], qi);                       /* :758 */
+            }
+        }
+    if (format == 0) orc_dcrt_ntt(rest, 0, tmp, B, 0);                   /* :759-760 / :807-808 */
+    for (size_t b = 0; b < B; b++)
+        for (uint32_t i = 0; i < l; i++) {
+            uint64_t qi = full->q[i];
+            const uint64_t* x = in + (b * T + i) * N;
+            const uint64_t* v = tmp + (b * l + i) * N;
+            uint64_t* o = out + (b * l + i) * N;
+            for (uint32_t n = 0; n < N; n++)
+                o[n] = t ? mulc1(orc_modadd_fast(x[n], mulc1(v[n], t, qi), qi), qlinv[i], qi)   /* :809-810 */
+                         : orc_modadd_fast(mulc1(x[n], qlinv[i], qi), v[n], qi);                /* :761-762 */
+        }
+    if (format == 1 && !t) orc_dcrt_ntt(rest, 0, out, B, 0);             /* :763-764: towers are switched, m_format is not */
+    free(lastp); free(tmp); free(c); free(qlinv);
+}
+
 int orc_max_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

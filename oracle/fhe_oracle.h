@@ -90,6 +90,29 @@ void orc_precompute_automap(uint32_t N, uint32_t k, uint32_t* map);
 void orc_automorphism_map(uint64_t* out, const uint64_t* in, uint32_t N, const uint32_t* map);
 int  orc_dcrt_automorphism(const orc_ctx* c, uint64_t* out, const uint64_t* in, size_t B, uint32_t k, int format);
 
+/* ---- RNS basis conversion and scaling, layouts [B][towers][N] ----
+ * Tables (plain modular arithmetic; equal to the BigInteger values of
+ * src/pke/lib/schemerns/rns-cryptoparameters.cpp:190-213 and ckksrns-cryptoparameters.cpp:66-88):
+ *   hat_inv[i] = (Q/q_i)^-1 mod q_i, hat_modp[i*sp+j] = (Q/q_i) mod p_j, Q = prod q_i
+ *   qlql[i] = floor(Ql * (Ql^-1 mod ql) / ql) mod q_i, qlinv[i] = ql^-1 mod q_i (l = T-1, Ql = prod_{i<l} q_i) */
+void orc_switch_tables(const uint64_t* q, uint32_t sq, const uint64_t* p, uint32_t sp, uint64_t* hat_inv, uint64_t* hat_modp);
+void orc_rescale_tables(const uint64_t* q, uint32_t T, uint64_t* qlql, uint64_t* qlinv);
+/* DCRTPolyImpl::ApproxSwitchCRTBasis (dcrtpoly-impl.h:1034-1082, HAVE_INT128 branch; Mul128 and
+ * BarrettUint128ModUint64 of utils/utilities-int.h:47-110) */
+void orc_approx_switch(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, const uint64_t* q, uint32_t sq,
+                       const uint64_t* p, uint32_t sp, const uint64_t* hat_inv, const uint64_t* hat_modp);
+/* DCRTPolyImpl::ApproxModUp (dcrtpoly-impl.h:1085-1133): in over Q (format 0 EVALUATION / 1 COEFFICIENT) ->
+ * out over QP in EVALUATION */
+void orc_approx_mod_up(const orc_ctx* Q, const orc_ctx* P, uint64_t* out, const uint64_t* in, size_t B, int format);
+/* DCRTPolyImpl::ApproxModDown (dcrtpoly-impl.h:1136-1175): in over QP, EVALUATION -> out over Q, EVALUATION;
+ * t = 0 (CKKS) or the plaintext modulus (BGV) */
+void orc_approx_mod_down(const orc_ctx* Q, const orc_ctx* P, uint64_t* out, const uint64_t* in, size_t B, uint64_t t);
+/* t = 0: DCRTPolyImpl::DropLastElementAndScale (dcrtpoly-impl.h:746-769); t > 0: DCRTPolyImpl::ModReduce
+ * (dcrtpoly-impl.h:792-812).  full = all T towers, rest = first T-1, last = tower T-1.  With format 1 the
+ * CKKS form returns forward-transformed towers, as the reference does (dcrtpoly-impl.h:765-766). */
+void orc_rescale(const orc_ctx* full, const orc_ctx* rest, const orc_ctx* last, uint64_t* out, const uint64_t* in,
+                 size_t B, int format, uint64_t t);
+
 /* ---- seeded input generator shared with the product's device-side fill
  * (counter based: value i depends only on (seed, i, q)) ---- */
 uint64_t orc_uniform_at(uint64_t seed, uint64_t i, uint64_t q);

@@ -32,6 +32,17 @@ struct ref_polys {
 
 static thread_local std::string g_ref_err;
 
+// The fork's PimManager / DpuMemory bookkeeping (every NativeVector constructs a PimData, mubintvecnat.h:128) is not
+// thread-safe (SURVEY §8(b) "Threading"), and these methods copy towers inside OpenMP loops.  Running the call on
+// thread 0 of a two-thread team makes the reference's inner `omp parallel for` regions nested, hence serial.
+template <class F>
+static void serial_omp(F f) {
+#pragma omp parallel num_threads(2)
+    {
+        if (omp_get_thread_num() == 0) f();
+    }
+}
+
 extern "C" {
 
 const char* ref_last_error(void) { return g_ref_err.c_str(); }
@@ -208,6 +219,168 @@ void ref_precompute_automap(uint32_t n, uint32_t k, uint32_t* out) {
     std::vector<uint32_t> map(n);
     PrecomputeAutoMap(n, k, &map);
     std::memcpy(out, map.data(), n * sizeof(uint32_t));
+}
+
+// ---- RNS basis conversion ---------------------------------------------------------
+// Tables are built the way the schemes' parameter code builds them, with the reference's BigInteger:
+//   [(Q/q_i)^-1]_{q_i}, [Q/q_i]_{p_j}                 src/pke/lib/schemerns/rns-cryptoparameters.cpp:199-213
+//   mu_j = floor(2^128 / p_j) as DoubleNativeInt      rns-cryptoparameters.cpp:273-283
+//   [P^-1]_{q_i}                                       rns-cryptoparameters.cpp:190-197
+//   rescale: [Ql*[Ql^-1]_{ql}/ql]_{qi}, [ql^-1]_{qi}  src/pke/lib/scheme/ckksrns/ckksrns-cryptoparameters.cpp:66-88
+struct ref_switch_tables {
+    std::vector<NativeInteger> hatInv, hatInvPrecon;
+    std::vector<std::vector<NativeInteger>> hatModp;
+    std::vector<DoubleNativeInt> mu;
+};
+static std::vector<NativeInteger> moduli_of(const ref_ctx* c) {
+    std::vector<NativeInteger> m;
+    for (auto& tp : c->params->GetParams()) m.push_back(tp->GetModulus());
+    return m;
+}
+static ref_switch_tables make_switch_tables(const std::vector<NativeInteger>& mq, const std::vector<NativeInteger>& mp) {
+    ref_switch_tables t;
+    BigInteger Q(1);
+    for (auto& q : mq) Q *= BigInteger(q);
+    size_t sq = mq.size(), sp = mp.size();
+    t.hatInv.resize(sq); t.hatInvPrecon.resize(sq); t.hatModp.resize(sq);
+    for (size_t i = 0; i < sq; i++) {
+        BigInteger hat    = Q / BigInteger(mq[i]);
+        t.hatInv[i]       = hat.ModInverse(BigInteger(mq[i])).ConvertToInt();
+        t.hatInvPrecon[i] = t.hatInv[i].PrepModMulConst(mq[i]);
+        t.hatModp[i].resize(sp);
+        for (size_t j = 0; j < sp; j++) t.hatModp[i][j] = hat.Mod(BigInteger(mp[j])).ConvertToInt();
+    }
+    const BigInteger B128("340282366920938463463374607431768211456"), T64("18446744073709551616");
+    t.mu.resize(sp);
+    for (size_t j = 0; j < sp; j++) {
+        BigInteger mu = B128 / BigInteger(mp[j]);
+        uint64_t val[2] = {(mu % T64).ConvertToInt(), mu.RShift(64).ConvertToInt()};
+        memcpy(&t.mu[j], val, sizeof(DoubleNativeInt));
+    }
+    return t;
+}
+// copies of the tables, for comparison with the backend's own: hat_inv [sq], hat_modp [sq][sp]
+void ref_switch_tables_get(const ref_ctx* from, const ref_ctx* to, uint64_t* hat_inv, uint64_t* hat_modp) {
+    auto t = make_switch_tables(moduli_of(from), moduli_of(to));
+    for (size_t i = 0; i < t.hatInv.size(); i++) {
+        hat_inv[i] = t.hatInv[i].ConvertToInt();
+        for (size_t j = 0; j < t.hatModp[i].size(); j++) hat_modp[i * t.hatModp[i].size() + j] = t.hatModp[i][j].ConvertToInt();
+    }
+}
+
+// DCRTPoly::ApproxSwitchCRTBasis (dcrtpoly-impl.h:1034-1082): batch over basis `from` -> new batch over `to`
+ref_polys* ref_polys_approx_switch(const ref_polys* a, ref_ctx* to) {
+    auto t  = make_switch_tables(moduli_of(a->ctx), moduli_of(to));
+    auto* r = new ref_polys{to, {}};
+    serial_omp([&] {
+        for (auto& poly : a->v)
+            r->v.push_back(poly.ApproxSwitchCRTBasis(a->ctx->params, to->params, t.hatInv, t.hatInvPrecon, t.hatModp, t.mu));
+    });
+    return r;
+}
+
+// DCRTPoly::ApproxModUp (dcrtpoly-impl.h:1085-1133), in place: the batch moves from basis Q to basis QP
+int ref_polys_approx_mod_up(ref_polys* a, ref_ctx* P, ref_ctx* QP) {
+    int rc = 0;
+    std::string err;
+    serial_omp([&] {
+        try {
+            auto t = make_switch_tables(moduli_of(a->ctx), moduli_of(P));
+            for (auto& poly : a->v)
+                poly.ApproxModUp(a->ctx->params, P->params, QP->params, t.hatInv, t.hatInvPrecon, t.hatModp, t.mu);
+            a->ctx = QP;
+        }
+        catch (const std::exception& e) { err = e.what(); rc = 1; }
+    });
+    if (rc) g_ref_err = err;
+    return rc;
+}
+
+// DCRTPoly::ApproxModDown (dcrtpoly-impl.h:1136-1175): batch over QP (EVALUATION) -> new batch over Q.
+// t = 0: CKKS form; t > 0: BGV form with [t^-1]_{p_j} (bgvrns-cryptoparameters.cpp:83-88).
+ref_polys* ref_polys_approx_mod_down(const ref_polys* a, ref_ctx* Q, ref_ctx* P, uint64_t t) {
+    ref_polys* res = nullptr;
+    std::string err;
+    serial_omp([&] {
+    try {
+        auto mq = moduli_of(Q), mp = moduli_of(P);
+        auto tb = make_switch_tables(mp, mq);
+        BigInteger modP(1);
+        for (auto& pj : mp) modP *= BigInteger(pj);
+        std::vector<NativeInteger> PInv(mq.size()), PInvPrecon(mq.size()), tInv(mp.size()), tInvPrecon(mp.size()), tModqPrecon(mq.size());
+        for (size_t i = 0; i < mq.size(); i++) {
+            PInv[i]       = modP.ModInverse(BigInteger(mq[i])).ConvertToInt();
+            PInvPrecon[i] = PInv[i].PrepModMulConst(mq[i]);
+            if (t) tModqPrecon[i] = NativeInteger(t).PrepModMulConst(mq[i]);
+        }
+        if (t)
+            for (size_t j = 0; j < mp.size(); j++) {
+                tInv[j]       = NativeInteger(t).ModInverse(mp[j]);
+                tInvPrecon[j] = tInv[j].PrepModMulConst(mp[j]);
+            }
+        auto* r = new ref_polys{Q, {}};
+        for (auto& poly : a->v)
+            r->v.push_back(poly.ApproxModDown(Q->params, P->params, PInv, PInvPrecon, tb.hatInv, tb.hatInvPrecon, tb.hatModp,
+                                              tb.mu, tInv, tInvPrecon, NativeInteger(t), tModqPrecon));
+        res = r;
+    }
+    catch (const std::exception& e) { err = e.what(); }
+    });
+    if (!res) g_ref_err = err;
+    return res;
+}
+
+// Rescale tables of level l = T-1 (ckksrns-cryptoparameters.cpp:66-88, k = 0)
+static void make_rescale_tables(const std::vector<NativeInteger>& mq, std::vector<NativeInteger>& c, std::vector<NativeInteger>& cPrecon,
+                                std::vector<NativeInteger>& qlInv, std::vector<NativeInteger>& qlInvPrecon) {
+    size_t l = mq.size() - 1;
+    BigInteger Ql(1);
+    for (size_t i = 0; i < l; i++) Ql *= BigInteger(mq[i]);
+    BigInteger QlInvModql = Ql.ModInverse(BigInteger(mq[l]));
+    BigInteger result     = (QlInvModql * Ql) / BigInteger(mq[l]);
+    c.resize(l); cPrecon.resize(l); qlInv.resize(l); qlInvPrecon.resize(l);
+    for (size_t i = 0; i < l; i++) {
+        c[i]           = result.Mod(BigInteger(mq[i])).ConvertToInt();
+        cPrecon[i]     = c[i].PrepModMulConst(mq[i]);
+        qlInv[i]       = mq[l].ModInverse(mq[i]);
+        qlInvPrecon[i] = qlInv[i].PrepModMulConst(mq[i]);
+    }
+}
+void ref_rescale_tables_get(const ref_ctx* c, uint64_t* qlql, uint64_t* qlinv) {
+    std::vector<NativeInteger> a, ap, b, bp;
+    make_rescale_tables(moduli_of(c), a, ap, b, bp);
+    for (size_t i = 0; i < a.size(); i++) { qlql[i] = a[i].ConvertToInt(); qlinv[i] = b[i].ConvertToInt(); }
+}
+
+// DCRTPoly::DropLastElementAndScale (dcrtpoly-impl.h:746-769, CKKS rescale; t = 0) or DCRTPoly::ModReduce
+// (dcrtpoly-impl.h:792-812, BGV modulus switching; t > 0), in place: the batch loses its last tower; `rest` is a
+// context over the first T-1 towers (used by ref_polys_store afterwards).
+int ref_polys_rescale(ref_polys* a, ref_ctx* rest, uint64_t t) {
+    int rc = 0;
+    std::string err;
+    serial_omp([&] {
+    try {
+        auto mq = moduli_of(a->ctx);
+        std::vector<NativeInteger> c, cPrecon, qlInv, qlInvPrecon;
+        make_rescale_tables(mq, c, cPrecon, qlInv, qlInvPrecon);
+        size_t l = mq.size() - 1;
+        for (auto& poly : a->v) {
+            if (t == 0) {
+                poly.DropLastElementAndScale(c, cPrecon, qlInv, qlInvPrecon);
+            } else {                                   // bgvrns-cryptoparameters.cpp:91-99, bgvrns-leveledshe.cpp:56-58
+                NativeInteger tt(t);
+                std::vector<NativeInteger> tModqPrecon(mq.size());
+                for (size_t i = 0; i < mq.size(); i++) tModqPrecon[i] = tt.PrepModMulConst(mq[i]);
+                NativeInteger negtInv = mq[l] - tt.ModInverse(mq[l]);
+                poly.ModReduce(tt, tModqPrecon, negtInv, negtInv.PrepModMulConst(mq[l]), qlInv, qlInvPrecon);
+            }
+        }
+        a->ctx = rest;
+    }
+    catch (const std::exception& e) { err = e.what(); rc = 1; }
+    });
+    if (rc) g_ref_err = err;
+    return rc;
 }
 
 // mod-ops of the PimData surface executed by the reference's own NativeVector (in-place forms:

@@ -44,6 +44,12 @@ class Oracle:
             ("orc_precompute_automap", None, [u32, u32, vp]),
             ("orc_automorphism_map", None, [vp, vp, u32, vp]),
             ("orc_dcrt_automorphism", ci, [vp, vp, vp, sz, u32, ci]),
+            ("orc_switch_tables", None, [vp, u32, vp, u32, vp, vp]),
+            ("orc_rescale_tables", None, [vp, u32, vp, vp]),
+            ("orc_approx_switch", None, [vp, vp, sz, u32, vp, u32, vp, u32, vp, vp]),
+            ("orc_approx_mod_up", None, [vp, vp, vp, vp, sz, ci]),
+            ("orc_approx_mod_down", None, [vp, vp, vp, vp, sz, u64]),
+            ("orc_rescale", None, [vp, vp, vp, vp, vp, sz, ci, u64]),
             ("orc_uniform_at", u64, [u64, u64, u64]), ("orc_fill_uniform", None, [vp, sz, u64, u64, u64]),
         ]:
             f = getattr(L, name)
@@ -157,6 +163,68 @@ def _automap(self, n, k):
 
 OracleCtx.automorphism = _automorphism
 Oracle.automap = _automap
+
+
+class OracleBasis:
+    """Two-basis helper: Q = first sq towers, P = the remaining sp of (q, psi); SURVEY §8(f) rank 3."""
+
+    def __init__(self, o, n, q, psi, sq):
+        self.o, self.n, self.sq, self.sp = o, n, sq, len(q) - sq
+        self.q, self.psi = np.ascontiguousarray(q, np.uint64), np.ascontiguousarray(psi, np.uint64)
+        self.Q = o.ctx(n, self.q[:sq].copy(), self.psi[:sq].copy())
+        self.P = o.ctx(n, self.q[sq:].copy(), self.psi[sq:].copy())
+
+    def tables(self, reverse=False):
+        a, b = (self.P, self.Q) if reverse else (self.Q, self.P)
+        hi, hm = np.empty(len(a.q), np.uint64), np.empty((len(a.q), len(b.q)), np.uint64)
+        self.o.L.orc_switch_tables(_p(a.q), len(a.q), _p(b.q), len(b.q), _p(hi), _p(hm))
+        return hi, hm
+
+    def approx_switch(self, x, reverse=False):
+        a, b = (self.P, self.Q) if reverse else (self.Q, self.P)
+        hi, hm = self.tables(reverse)
+        x = np.ascontiguousarray(x, np.uint64)
+        B = x.size // (len(a.q) * self.n)
+        out = np.empty((B, len(b.q), self.n), np.uint64)
+        self.o.L.orc_approx_switch(_p(out), _p(x), B, self.n, _p(a.q), len(a.q), _p(b.q), len(b.q), _p(hi), _p(hm))
+        return out
+
+    def mod_up(self, x, fmt):
+        x = np.ascontiguousarray(x, np.uint64)
+        B = x.size // (self.sq * self.n)
+        out = np.empty((B, self.sq + self.sp, self.n), np.uint64)
+        self.o.L.orc_approx_mod_up(self.Q.h, self.P.h, _p(out), _p(x), B, fmt)
+        return out
+
+    def mod_down(self, x, t=0):
+        x = np.ascontiguousarray(x, np.uint64)
+        B = x.size // ((self.sq + self.sp) * self.n)
+        out = np.empty((B, self.sq, self.n), np.uint64)
+        self.o.L.orc_approx_mod_down(self.Q.h, self.P.h, _p(out), _p(x), B, t)
+        return out
+
+
+def _rescale(self, n, q, psi, x, fmt, t=0):
+    """DropLastElementAndScale (t = 0) / ModReduce (t > 0) over all len(q) towers."""
+    q, psi = np.ascontiguousarray(q, np.uint64), np.ascontiguousarray(psi, np.uint64)
+    full, rest, last = self.ctx(n, q, psi), self.ctx(n, q[:-1].copy(), psi[:-1].copy()), self.ctx(n, q[-1:].copy(), psi[-1:].copy())
+    x = np.ascontiguousarray(x, np.uint64)
+    B = x.size // (len(q) * n)
+    out = np.empty((B, len(q) - 1, n), np.uint64)
+    self.L.orc_rescale(full.h, rest.h, last.h, _p(out), _p(x), B, fmt, t)
+    return out
+
+
+def _rescale_tables(self, q):
+    q = np.ascontiguousarray(q, np.uint64)
+    a, b = np.empty(len(q) - 1, np.uint64), np.empty(len(q) - 1, np.uint64)
+    self.L.orc_rescale_tables(_p(q), len(q), _p(a), _p(b))
+    return a, b
+
+
+Oracle.rescale = _rescale
+Oracle.rescale_tables = _rescale_tables
+Oracle.basis = lambda self, n, q, psi, sq: OracleBasis(self, n, q, psi, sq)
 
 
 def load():

@@ -34,6 +34,14 @@ def ref():
     R.ref_polys_automorphism.argtypes = [vp, u32, ci]
     R.ref_precompute_automap.argtypes = [u32, u32, vp]
     R.ref_last_error.restype = ctypes.c_char_p
+    R.ref_polys_approx_switch.restype = vp
+    R.ref_polys_approx_switch.argtypes = [vp, vp]
+    R.ref_polys_approx_mod_up.argtypes = [vp, vp, vp]
+    R.ref_polys_approx_mod_down.restype = vp
+    R.ref_polys_approx_mod_down.argtypes = [vp, vp, vp, u64]
+    R.ref_polys_rescale.argtypes = [vp, vp, u64]
+    R.ref_switch_tables_get.argtypes = [vp, vp, vp, vp]
+    R.ref_rescale_tables_get.argtypes = [vp, vp, vp]
     return R
 
 
@@ -113,3 +121,60 @@ def test_automorphism_matches_reference(oracle, ref, n, towers):
     assert not ref.ref_polys_automorphism(ha, 4, 0) and b"not odd" in ref.ref_last_error()
     ref.ref_polys_free(ha)
     ref.ref_ctx_destroy(ctx)
+
+
+@pytest.mark.parametrize("nbits,n,sq,sp", [(30, 16, 2, 1), (60, 64, 3, 2), (60, 1 << 10, 5, 3), (45, 1 << 12, 2, 4)])
+def test_basis_conversion_matches_reference(oracle, ref, nbits, n, sq, sp):
+    """ApproxSwitchCRTBasis, ApproxModUp, ApproxModDown (CKKS and BGV forms),
+    DropLastElementAndScale and ModReduce of the reference's DCRTPoly vs the restatement, and the tables
+    against the BigInteger values the schemes' parameter code computes."""
+    q, psi = oracle.gen_params(nbits, n, sq + sp)
+    ob = oracle.basis(n, q, psi, sq)
+    mk = lambda a, b: ref.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+    cQ, cP, cQP, cR = mk(0, sq), mk(sq, sq + sp), mk(0, sq + sp), mk(0, sq + sp - 1)
+    B = 2
+    for rev, (ca, cb) in ((False, (cQ, cP)), (True, (cP, cQ))):
+        hi, hm = ob.tables(rev)
+        rhi, rhm = np.empty_like(hi), np.empty_like(hm)
+        ref.ref_switch_tables_get(ca, cb, p(rhi), p(rhm))
+        assert np.array_equal(hi, rhi) and np.array_equal(hm, rhm)
+    a, b = oracle.rescale_tables(q)
+    ra, rb = np.empty_like(a), np.empty_like(b)
+    ref.ref_rescale_tables_get(cQP, p(ra), p(rb))
+    assert np.array_equal(a, ra) and np.array_equal(b, rb)
+
+    x = oracle.fill_ring(B, n, q[:sq].copy(), 11)
+    x[0, :, 0] = q[:sq] - 1
+    x[0, :, 1] = 0
+    hx = ref.ref_polys_load(cQ, p(x), B, 1)
+    hr = ref.ref_polys_approx_switch(hx, cP)
+    res = np.empty((B, sp, n), np.uint64)
+    ref.ref_polys_store(hr, p(res))
+    assert np.array_equal(res, ob.approx_switch(x))
+    ref.ref_polys_free(hr); ref.ref_polys_free(hx)
+    for fmt in (0, 1):
+        hx = ref.ref_polys_load(cQ, p(x), B, fmt)
+        assert ref.ref_polys_approx_mod_up(hx, cP, cQP) == 0, ref.ref_last_error()
+        res = np.empty((B, sq + sp, n), np.uint64)
+        ref.ref_polys_store(hx, p(res))
+        assert np.array_equal(res, ob.mod_up(x, fmt)), f"ApproxModUp format {fmt}"
+        ref.ref_polys_free(hx)
+    y = oracle.fill_ring(B, n, q, 12)
+    y[0, :, 0] = q - 1
+    for t in (0, 65537, 2):
+        hy = ref.ref_polys_load(cQP, p(y), B, 0)
+        hr = ref.ref_polys_approx_mod_down(hy, cQ, cP, t)
+        assert hr, ref.ref_last_error()
+        res = np.empty((B, sq, n), np.uint64)
+        ref.ref_polys_store(hr, p(res))
+        assert np.array_equal(res, ob.mod_down(y, t)), f"ApproxModDown t={t}"
+        ref.ref_polys_free(hr); ref.ref_polys_free(hy)
+        for fmt in (0, 1):
+            hy = ref.ref_polys_load(cQP, p(y), B, fmt)
+            assert ref.ref_polys_rescale(hy, cR, t) == 0, ref.ref_last_error()
+            res = np.empty((B, sq + sp - 1, n), np.uint64)
+            ref.ref_polys_store(hy, p(res))
+            assert np.array_equal(res, oracle.rescale(n, q, psi, y, fmt, t)), f"rescale t={t} format {fmt}"
+            ref.ref_polys_free(hy)
+    for c in (cQ, cP, cQP, cR):
+        ref.ref_ctx_destroy(c)
