@@ -28,6 +28,10 @@
  *     transformnat-impl.h:708-763
  *   DCRTPolyImpl::AutomorphismTransform (k) / (k, precomp)       fhe_automorphism / fhe_automorphism_map
  *     dcrtpoly-impl.h:348-369, poly-impl.h:312-380
+ *   DCRTPolyImpl::ApproxSwitchCRTBasis / ApproxModUp /          fhe_approx_switch_crt_basis / fhe_approx_mod_up /
+ *     ApproxModDown   dcrtpoly-impl.h:1034-1175                   fhe_approx_mod_down
+ *   DCRTPolyImpl::DropLastElementAndScale / ModReduce            fhe_drop_last_element_and_scale / fhe_mod_reduce
+ *     dcrtpoly-impl.h:746-812
  *   FirstPrime / PreviousPrime / RootOfUnity parameter recipe    fhe_gen_params (host side, setup only)
  *     math/nbtheory-impl.h:183-231,334-379;
  *     benchmark/src/poly-benchmark-16k.cpp:82-101
@@ -156,6 +160,49 @@ int fhe_automorphism(fhe_ring* ring, fhe_dptr dst, fhe_dptr src, size_t batch, u
 int fhe_precompute_automap(uint32_t N, uint32_t k, uint32_t* map);
 /* The two-argument form (poly-impl.h:368-380): dst[j] = src[map[j]] per tower, map = N uint32 in HBM. */
 int fhe_automorphism_map(fhe_ring* ring, fhe_dptr dst, fhe_dptr src, size_t batch, fhe_dptr map, int stream);
+/* ---- RNS basis conversion and scaling ---------------------------------- */
+/* A ring over towers [first, first+count) of `parent`, sharing its constant tables (no copy); the parent must
+ * outlive the view.  ILDCRTParams of a sub-basis (e.g. Q and P inside QP). */
+int fhe_ring_view(fhe_ring* parent, uint32_t first, uint32_t count, fhe_ring** out);
+
+typedef struct fhe_basis fhe_basis;  /* tables of ApproxSwitchCRTBasis from one ring's moduli to another's */
+/* qhat_inv_modq [sq] = [(Q/q_i)^-1]_{q_i} and qhat_modp [sq][sp] = [Q/q_i]_{p_j} as the schemes precompute them
+ * (src/pke/lib/schemerns/rns-cryptoparameters.cpp:199-229); either may be NULL, then it is derived from the
+ * moduli.  Shoup companions and the 128-bit Barrett constants (rns-cryptoparameters.cpp:273-283) are built here.
+ * Both rings must have the same N and live on the same context; they must outlive the basis.  A basis keeps
+ * scratch buffers, so use one per stream. */
+int fhe_basis_create(fhe_ring* from, fhe_ring* to, const uint64_t* qhat_inv_modq, const uint64_t* qhat_modp,
+                     fhe_basis** out);
+int fhe_basis_destroy(fhe_basis* basis);
+/* host copies of the two tables in use */
+int fhe_basis_tables(const fhe_basis* basis, uint64_t* qhat_inv_modq, uint64_t* qhat_modp);
+/* DCRTPolyImpl::ApproxSwitchCRTBasis (dcrtpoly-impl.h:1034-1082): src over `from` [batch][sq][N] ->
+ * dst over `to` [batch][sp][N]; the format is whatever src is in (the schemes call it in COEFFICIENT). */
+int fhe_approx_switch_crt_basis(fhe_basis* basis, fhe_dptr dst, fhe_dptr src, size_t batch, int stream);
+/* DCRTPolyImpl::ApproxModUp (dcrtpoly-impl.h:1085-1133) with basis = Q -> P: src over Q in `format`
+ * (0 EVALUATION, 1 COEFFICIENT) -> dst over QP [batch][sq+sp][N] in EVALUATION.  src is not modified. */
+int fhe_approx_mod_up(fhe_basis* q_to_p, fhe_dptr dst_qp, fhe_dptr src_q, size_t batch, int format, int stream);
+/* DCRTPolyImpl::ApproxModDown (dcrtpoly-impl.h:1136-1175) with basis = P -> Q: src over QP [batch][sq+sp][N]
+ * in EVALUATION -> dst over Q in EVALUATION.  t = 0: CKKS form; t > 0: BGV form (multiplies the P part by
+ * [t^-1]_{p_j} and the switched part by t, bgvrns-cryptoparameters.cpp:83-88).  [P^-1]_{q_i}
+ * (rns-cryptoparameters.cpp:190-197) is derived from the moduli. */
+int fhe_approx_mod_down(fhe_basis* p_to_q, fhe_dptr dst_q, fhe_dptr src_qp, size_t batch, uint64_t t, int stream);
+
+typedef struct fhe_rescale fhe_rescale;  /* constants for dropping the last tower of `ring` */
+/* qlql [T-1] = [Ql*[Ql^-1]_{ql}/ql]_{q_i} and qlinv [T-1] = [ql^-1]_{q_i}
+ * (src/pke/lib/scheme/ckksrns/ckksrns-cryptoparameters.cpp:66-88); NULL -> derived from the moduli.
+ * The ring must have >= 2 towers and outlive the plan; one plan per stream. */
+int fhe_rescale_create(fhe_ring* ring, const uint64_t* qlql, const uint64_t* qlinv, fhe_rescale** out);
+int fhe_rescale_destroy(fhe_rescale* plan);
+int fhe_rescale_tables(const fhe_rescale* plan, uint64_t* qlql, uint64_t* qlinv);
+/* DCRTPolyImpl::DropLastElementAndScale (dcrtpoly-impl.h:746-769, CKKS rescale): src [batch][T][N] in `format`
+ * -> dst [batch][T-1][N].  With format 1 (COEFFICIENT) the towers come back forward-transformed, as the
+ * reference leaves them (dcrtpoly-impl.h:765-766). */
+int fhe_drop_last_element_and_scale(fhe_rescale* plan, fhe_dptr dst, fhe_dptr src, size_t batch, int format, int stream);
+/* DCRTPolyImpl::ModReduce (dcrtpoly-impl.h:792-812, BGV modulus switching) with plaintext modulus t > 0;
+ * [-t^-1]_{ql} and [t]_{q_i} (bgvrns-cryptoparameters.cpp:91-99) are derived here.  Format is preserved. */
+int fhe_mod_reduce(fhe_rescale* plan, fhe_dptr dst, fhe_dptr src, size_t batch, uint64_t t, int format, int stream);
+
 /* seeded uniform coefficients in [0, q_tower) (synthetic inputs for tests and benchmarks) */
 int fhe_fill_uniform(fhe_ring* ring, fhe_dptr dst, size_t batch, uint64_t seed, int stream);
 

@@ -30,6 +30,67 @@ def digest(a):
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 
 
+BASIS_CASES = [  # nbits, N, sizeQ, sizeP, batch, seed
+    (30, 16, 2, 1, 2, 20262001),
+    (60, 1 << 10, 4, 2, 2, 20262002),
+    (60, 1 << 14, 5, 3, 1, 20262003),
+]
+
+
+def basis_section(R, O, p):
+    """Section "basis": digests of ApproxSwitchCRTBasis, ApproxModUp, ApproxModDown (t = 0 and 65537),
+    DropLastElementAndScale and ModReduce (dcrtpoly-impl.h:746-812, 1034-1175) run by the reference, tables built
+    with its BigInteger as the schemes do (oracle/ref_driver.cpp)."""
+    R.ref_polys_approx_switch.restype = vp
+    R.ref_polys_approx_switch.argtypes = [vp, vp]
+    R.ref_polys_approx_mod_up.argtypes = [vp, vp, vp]
+    R.ref_polys_approx_mod_down.restype = vp
+    R.ref_polys_approx_mod_down.argtypes = [vp, vp, vp, u64]
+    R.ref_polys_rescale.argtypes = [vp, vp, u64]
+    out = []
+    for nbits, n, sq, sp, batch, seed in BASIS_CASES:
+        q, psi = np.zeros(sq + sp, np.uint64), np.zeros(sq + sp, np.uint64)
+        R.ref_gen_params(nbits, n, sq + sp, p(q), p(psi))
+        mk = lambda a, b: R.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+        cQ, cP, cQP, cR = mk(0, sq), mk(sq, sq + sp), mk(0, sq + sp), mk(0, sq + sp - 1)
+        x = O.fill_ring(batch, n, q[:sq].copy(), seed)
+        y = O.fill_ring(batch, n, q, seed + 1)
+        rec = {"nbits": nbits, "N": n, "sizeQ": sq, "sizeP": sp, "batch": batch, "seed": seed,
+               "q": [int(v) for v in q], "psi": [int(v) for v in psi], "sha_x": digest(x), "sha_y": digest(y)}
+        hx = R.ref_polys_load(cQ, p(x), batch, 1)
+        hr = R.ref_polys_approx_switch(hx, cP)
+        res = np.empty((batch, sp, n), np.uint64)
+        R.ref_polys_store(hr, p(res))
+        rec["sha_switch"] = digest(res)
+        R.ref_polys_free(hr); R.ref_polys_free(hx)
+        for fmt in (0, 1):
+            hx = R.ref_polys_load(cQ, p(x), batch, fmt)
+            assert R.ref_polys_approx_mod_up(hx, cP, cQP) == 0
+            res = np.empty((batch, sq + sp, n), np.uint64)
+            R.ref_polys_store(hx, p(res))
+            rec[f"sha_modup_f{fmt}"] = digest(res)
+            R.ref_polys_free(hx)
+        for t in (0, 65537):
+            hy = R.ref_polys_load(cQP, p(y), batch, 0)
+            hr = R.ref_polys_approx_mod_down(hy, cQ, cP, t)
+            res = np.empty((batch, sq, n), np.uint64)
+            R.ref_polys_store(hr, p(res))
+            rec[f"sha_moddown_t{t}"] = digest(res)
+            R.ref_polys_free(hr); R.ref_polys_free(hy)
+            for fmt in (0, 1):
+                hy = R.ref_polys_load(cQP, p(y), batch, fmt)
+                assert R.ref_polys_rescale(hy, cR, t) == 0
+                res = np.empty((batch, sq + sp - 1, n), np.uint64)
+                R.ref_polys_store(hy, p(res))
+                rec[f"sha_rescale_t{t}_f{fmt}"] = digest(res)
+                R.ref_polys_free(hy)
+        for c in (cQ, cP, cQP, cR):
+            R.ref_ctx_destroy(c)
+        out.append(rec)
+        print("basis case", n, sq, sp, "done")
+    return out
+
+
 def main():
     R = ctypes.CDLL(oracle_py.REF_SO)
     R.ref_gen_params.argtypes = [u32, u32, u32, vp, vp]
@@ -71,6 +132,7 @@ def main():
         R.ref_ctx_destroy(ctx)
         auto.append(rec)
         print("automorphism case", n, towers, "done")
+    basis = basis_section(R, O, p)
     path = os.path.join(ROOT, "tests", "golden", "ext_vectors.json")
     doc = {}
     if os.path.exists(path):
@@ -79,6 +141,7 @@ def main():
     doc["generator"] = ("tests/golden/make_golden_ext.py over oracle/_ref/libopenfhe_ref.so "
                         "(reference commit e70da11 compiled by oracle/Makefile)")
     doc["automorphism"] = auto
+    doc["basis"] = basis
     with open(path, "w") as f:
         json.dump(doc, f, indent=1)
     print("wrote", path)

@@ -54,6 +54,18 @@ SIGNATURES = {
     "fhe_automorphism": (ci, [vp, u64, u64, sz, u32, ci, ci]),
     "fhe_precompute_automap": (ci, [u32, u32, vp]),
     "fhe_automorphism_map": (ci, [vp, u64, u64, sz, u64, ci]),
+    "fhe_ring_view": (ci, [vp, u32, u32, ctypes.POINTER(vp)]),
+    "fhe_basis_create": (ci, [vp, vp, vp, vp, ctypes.POINTER(vp)]),
+    "fhe_basis_destroy": (ci, [vp]),
+    "fhe_basis_tables": (ci, [vp, vp, vp]),
+    "fhe_approx_switch_crt_basis": (ci, [vp, u64, u64, sz, ci]),
+    "fhe_approx_mod_up": (ci, [vp, u64, u64, sz, ci, ci]),
+    "fhe_approx_mod_down": (ci, [vp, u64, u64, sz, u64, ci]),
+    "fhe_rescale_create": (ci, [vp, vp, vp, ctypes.POINTER(vp)]),
+    "fhe_rescale_destroy": (ci, [vp]),
+    "fhe_rescale_tables": (ci, [vp, vp, vp]),
+    "fhe_drop_last_element_and_scale": (ci, [vp, u64, u64, sz, ci, ci]),
+    "fhe_mod_reduce": (ci, [vp, u64, u64, sz, u64, ci, ci]),
     "fhe_fill_uniform": (ci, [vp, u64, sz, u64, ci]),
     "fhe_vec_op": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),
     "fhe_vec_op_scalar": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),

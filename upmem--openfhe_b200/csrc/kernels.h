@@ -43,6 +43,29 @@ cudaError_t launch_automorphism(const RingDev& r, uint64_t* dst, const uint64_t*
 // dst[j] = src[map[j]] per tower (map: N uint32 in HBM), the precomputed-table form.
 cudaError_t launch_automorphism_map(const RingDev& r, uint64_t* dst, const uint64_t* src, size_t batch,
                                     const uint32_t* map, cudaStream_t st);
+// ---- RNS basis conversion (basis.cu) ----
+struct BasisTarget {             // one target modulus p_j of ApproxSwitchCRTBasis
+    uint64_t p, mu_lo, mu_hi;    // mu = floor(2^128 / p) (utils/utilities-int.h:60)
+    uint64_t post, postp;        // optional multiplier applied to the reduced value (0 = none) and its Shoup companion
+    uint64_t pad[3];
+};
+struct BasisDev {
+    uint32_t sq, sp;
+    const uint64_t* q;           // [sq] source moduli
+    const ulonglong2* pre;       // [sq] {[(Q/q_i)^-1]_{q_i} (times an optional scalar), Shoup companion}
+    const uint64_t* hat;         // [sq][sp] [Q/q_i]_{p_j}
+    const BasisTarget* tgt;      // [sp]
+};
+// dst towers dst0.. of [batch][dstT][N] = ApproxSwitchCRTBasis of src towers src0..src0+sq-1 of [batch][srcT][N]
+cudaError_t launch_basis_switch(const BasisDev& bd, uint64_t* dst, uint32_t dstT, uint32_t dst0, const uint64_t* src,
+                                uint32_t srcT, uint32_t src0, size_t batch, uint32_t logN, cudaStream_t st);
+// mode 0: out = (x - v) * c; 1: out = x * c + v; 2: out = (x + v * t) * c, per tower k[i] = {c, c', t, t'};
+// x from [batch][xT][N] (towers 0..l-1), v and out over [batch][l][N]
+cudaError_t launch_tower_affine(int mode, uint64_t* out, const uint64_t* x, const uint64_t* v, size_t batch, uint32_t logN,
+                                uint32_t l, uint32_t xT, const TowerMod* mods, const ulonglong4* k, cudaStream_t st);
+// tmp[b][i][n] = SwitchModulus(last[b][n], ql -> q_i) (* c_i), see basis.cu
+cudaError_t launch_rescale_spread(uint64_t* tmp, const uint64_t* last, size_t batch, uint32_t logN, uint32_t l, uint64_t ql,
+                                  const ulonglong4* sw, const ulonglong4* k, ulonglong2 pre, int bgv, cudaStream_t st);
 // Counter-based uniform fill in [0, q_t) per tower (same definition as the test oracle's generator).
 cudaError_t launch_fill_uniform(const RingDev& r, uint64_t* dst, size_t batch, uint64_t seed,
                                 cudaStream_t st);

@@ -750,6 +750,391 @@ extern "C" int fhe_launch(fhe_ctx* ctx, int kernel_id, const void* desc, fhe_dpt
 }
 
 // ---------------------------------------------------------------------------------------------
+// RNS basis conversion and scaling
+// ---------------------------------------------------------------------------------------------
+extern "C" int fhe_ring_view(fhe_ring* parent, uint32_t first, uint32_t count, fhe_ring** out) {
+    if (!parent || !out) return fail(FHE_EINVAL, "fhe_ring_view: null argument");
+    *out = nullptr;
+    if (count == 0 || first + count > parent->dev.T || first + count < first)
+        return fail(FHE_EINVAL, "fhe_ring_view: towers [%u, %u) not inside the parent's %u", first, first + count, parent->dev.T);
+    auto* r = new fhe_ring;
+    r->ctx = parent->ctx;
+    r->dev = parent->dev;
+    r->dev.T = count;
+    r->dev.mods = parent->dev.mods + first;
+    if (parent->dev.twF) r->dev.twF = parent->dev.twF + (size_t)first * parent->dev.N;
+    if (parent->dev.twI) r->dev.twI = parent->dev.twI + (size_t)first * parent->dev.N;
+    if (parent->dev.invc) r->dev.invc = parent->dev.invc + 2 * (size_t)first;
+    r->q.assign(parent->q.begin() + first, parent->q.begin() + first + count);
+    if (!parent->psi.empty()) r->psi.assign(parent->psi.begin() + first, parent->psi.begin() + first + count);
+    r->has_ntt = parent->has_ntt;
+    r->ntt_identity = parent->ntt_identity;
+    *out = r;                                  // owns no device memory: fhe_ring_destroy only deletes the handle
+    return FHE_OK;
+}
+
+namespace {
+// grow-only device scratch owned by a plan; released when the plan is destroyed
+struct Scratch {
+    void* p = nullptr;
+    size_t bytes = 0;
+    int need(fhe_ctx* ctx, size_t n) {
+        if (n <= bytes) return FHE_OK;
+        if (p) { cudaDeviceSynchronize(); ctx->arena.release(p); p = nullptr; bytes = 0; }
+        int rc = ctx->arena.alloc(n, &p);
+        if (rc) return rc;
+        bytes = n;
+        return FHE_OK;
+    }
+    void drop(fhe_ctx* ctx) { if (p) ctx->arena.release(p); p = nullptr; bytes = 0; }
+};
+
+template <class T>
+int upload(fhe_ctx* ctx, const std::vector<T>& h, void** d) {
+    if (!*d) {
+        int rc = ctx->arena.alloc(std::max<size_t>(h.size() * sizeof(T), 16), d);
+        if (rc) return rc;
+    }
+    cudaError_t e = cudaMemcpy(*d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
+    return e == cudaSuccess ? FHE_OK : fail(FHE_ECUDA, "upload constants: %s", cudaGetErrorString(e));
+}
+
+uint64_t prod_mod(const std::vector<uint64_t>& f, size_t skip, uint64_t m) {   // prod_{k != skip} f[k] mod m
+    uint64_t r = 1 % m;
+    for (size_t k = 0; k < f.size(); k++)
+        if (k != skip) r = host::mulmod(r, f[k] % m, m);
+    return r;
+}
+}  // namespace
+
+struct fhe_basis {
+    fhe_ctx* ctx = nullptr;
+    fhe_ring *from = nullptr, *to = nullptr;
+    std::vector<uint64_t> hat_inv, hat_modp;      // [sq], [sq][sp]
+    BasisDev dev{};                               // plain tables (t = 0)
+    void *d_q = nullptr, *d_pre = nullptr, *d_hat = nullptr, *d_tgt = nullptr;
+    // ApproxModDown extras: [P^-1]_{q_i} records and the t-folded variant of pre / tgt (cached for the last t)
+    void *d_pinv = nullptr, *d_pre_t = nullptr, *d_tgt_t = nullptr;
+    uint64_t t_cached = 0;
+    bool pinv_ready = false;
+    Scratch s0, s1;
+};
+
+static void basis_fill(const fhe_basis* b, uint64_t t, std::vector<ulonglong2>& pre, std::vector<BasisTarget>& tgt) {
+    const auto& q = b->from->q;
+    const auto& p = b->to->q;
+    pre.resize(q.size());
+    tgt.resize(p.size());
+    for (size_t i = 0; i < q.size(); i++) {
+        uint64_t c = b->hat_inv[i] % q[i];
+        if (t) c = host::mulmod(c, host::invmod(t % q[i], q[i]), q[i]);     // partP *= [t^-1]_{p_j} folded in
+        pre[i] = make_ulonglong2(c, host::shoup_companion(c, q[i]));
+    }
+    for (size_t j = 0; j < p.size(); j++) {
+        BasisTarget g{};
+        g.p = p[j];
+        unsigned __int128 mu = (~(unsigned __int128)0) / p[j];              // floor(2^128 / p): p is not a power of two
+        g.mu_lo = (uint64_t)mu;
+        g.mu_hi = (uint64_t)(mu >> 64);
+        if (t) { g.post = t % p[j]; g.postp = host::shoup_companion(g.post, p[j]); }
+        tgt[j] = g;
+    }
+}
+
+extern "C" int fhe_basis_destroy(fhe_basis* b) {
+    if (!b) return FHE_OK;
+    cudaSetDevice(b->ctx->device);
+    cudaDeviceSynchronize();
+    for (void* p : {b->d_q, b->d_pre, b->d_hat, b->d_tgt, b->d_pinv, b->d_pre_t, b->d_tgt_t})
+        if (p) b->ctx->arena.release(p);
+    b->s0.drop(b->ctx);
+    b->s1.drop(b->ctx);
+    delete b;
+    return FHE_OK;
+}
+
+extern "C" int fhe_basis_create(fhe_ring* from, fhe_ring* to, const uint64_t* qhat_inv_modq, const uint64_t* qhat_modp,
+                                fhe_basis** out) {
+    if (!from || !to || !out) return fail(FHE_EINVAL, "fhe_basis_create: null argument");
+    *out = nullptr;
+    if (from->ctx != to->ctx) return fail(FHE_EINVAL, "fhe_basis_create: rings live on different contexts");
+    if (from->dev.N != to->dev.N) return fail(FHE_EINVAL, "fhe_basis_create: ring dimensions differ");
+    const size_t sq = from->q.size(), sp = to->q.size();
+    for (uint64_t p : to->q)
+        if ((p & (p - 1)) == 0) return fail(FHE_EINVAL, "fhe_basis_create: target modulus %llu is a power of two", (unsigned long long)p);
+    CUDA_TRY(cudaSetDevice(from->ctx->device));
+    auto* b = new fhe_basis;
+    b->ctx = from->ctx; b->from = from; b->to = to;
+    b->hat_inv.resize(sq);
+    b->hat_modp.resize(sq * sp);
+    for (size_t i = 0; i < sq; i++) {
+        if (qhat_inv_modq) {
+            b->hat_inv[i] = qhat_inv_modq[i];
+        } else {
+            uint64_t h = prod_mod(from->q, i, from->q[i]);
+            if (h == 0 || std::__gcd(h, from->q[i]) != 1) {
+                delete b;
+                return fail(FHE_EINVAL, "fhe_basis_create: source moduli are not pairwise coprime (tower %zu)", i);
+            }
+            b->hat_inv[i] = host::invmod(h, from->q[i]);
+        }
+        for (size_t j = 0; j < sp; j++)
+            b->hat_modp[i * sp + j] = qhat_modp ? qhat_modp[i * sp + j] : prod_mod(from->q, i, to->q[j]);
+    }
+    std::vector<ulonglong2> pre;
+    std::vector<BasisTarget> tgt;
+    basis_fill(b, 0, pre, tgt);
+    int rc;
+    if ((rc = upload(b->ctx, from->q, &b->d_q)) || (rc = upload(b->ctx, pre, &b->d_pre)) ||
+        (rc = upload(b->ctx, b->hat_modp, &b->d_hat)) || (rc = upload(b->ctx, tgt, &b->d_tgt))) {
+        fhe_basis_destroy(b);
+        return rc;
+    }
+    b->dev.sq = (uint32_t)sq; b->dev.sp = (uint32_t)sp;
+    b->dev.q = (const uint64_t*)b->d_q;
+    b->dev.pre = (const ulonglong2*)b->d_pre;
+    b->dev.hat = (const uint64_t*)b->d_hat;
+    b->dev.tgt = (const BasisTarget*)b->d_tgt;
+    *out = b;
+    return FHE_OK;
+}
+
+extern "C" int fhe_basis_tables(const fhe_basis* b, uint64_t* qhat_inv_modq, uint64_t* qhat_modp) {
+    if (!b) return fail(FHE_EINVAL, "null basis");
+    if (qhat_inv_modq) memcpy(qhat_inv_modq, b->hat_inv.data(), b->hat_inv.size() * 8);
+    if (qhat_modp) memcpy(qhat_modp, b->hat_modp.data(), b->hat_modp.size() * 8);
+    return FHE_OK;
+}
+
+extern "C" int fhe_approx_switch_crt_basis(fhe_basis* b, fhe_dptr dst, fhe_dptr src, size_t batch, int stream) {
+    if (!b) return fail(FHE_EINVAL, "null basis");
+    cudaStream_t s;
+    int rc = ring_stream(b->from, stream, &s);
+    if (rc) return rc;
+    if (batch == 0) return FHE_OK;
+    if (!dst || !src) return fail(FHE_EINVAL, "fhe_approx_switch_crt_basis: null device pointer");
+    CUDA_TRY(launch_basis_switch(b->dev, (uint64_t*)(uintptr_t)dst, b->dev.sp, 0, (const uint64_t*)(uintptr_t)src, b->dev.sq, 0,
+                                 batch, b->from->dev.logN, s));
+    return FHE_OK;
+}
+
+// strided tower copy between [batch][dT][N] (towers d0..) and [batch][sT][N] (towers s0..), cnt towers per item
+static cudaError_t copy_towers(uint64_t* dst, uint32_t dT, uint32_t d0, const uint64_t* src, uint32_t sT, uint32_t s0,
+                               uint32_t cnt, size_t batch, uint32_t N, cudaStream_t s) {
+    return cudaMemcpy2DAsync(dst + (size_t)d0 * N, (size_t)dT * N * 8, src + (size_t)s0 * N, (size_t)sT * N * 8,
+                             (size_t)cnt * N * 8, batch, cudaMemcpyDeviceToDevice, s);
+}
+
+static int ring_ntt(fhe_ring* r, uint64_t* x, size_t batch, bool inverse, cudaStream_t s, const char* who) {
+    if (r->ntt_identity || r->dev.N == 1) return FHE_OK;
+    if (!r->has_ntt) return fail(FHE_EINVAL, "%s: a ring was created without roots of unity", who);
+    CUDA_TRY(launch_ntt(r->dev, x, batch, inverse, s, 0));
+    return FHE_OK;
+}
+
+extern "C" int fhe_approx_mod_up(fhe_basis* b, fhe_dptr dst_qp, fhe_dptr src_q, size_t batch, int format, int stream) {
+    if (!b) return fail(FHE_EINVAL, "null basis");
+    cudaStream_t s;
+    int rc = ring_stream(b->from, stream, &s);
+    if (rc) return rc;
+    if (format != 0 && format != 1) return fail(FHE_EINVAL, "fhe_approx_mod_up: format must be 0 or 1");
+    if (batch == 0) return FHE_OK;
+    if (!dst_qp || !src_q) return fail(FHE_EINVAL, "fhe_approx_mod_up: null device pointer");
+    const uint32_t N = b->from->dev.N, logN = b->from->dev.logN, sq = b->dev.sq, sp = b->dev.sp;
+    uint64_t* dst = (uint64_t*)(uintptr_t)dst_qp;
+    const uint64_t* src = (const uint64_t*)(uintptr_t)src_q;
+    const size_t wq = batch * sq * (size_t)N, wp = batch * sp * (size_t)N;
+    if ((rc = b->s0.need(b->ctx, wq * 8)) || (rc = b->s1.need(b->ctx, wp * 8))) return rc;
+    uint64_t* coef = (uint64_t*)b->s0.p;
+    uint64_t* partP = (uint64_t*)b->s1.p;
+    // COEFFICIENT form of the Q towers (dcrtpoly-impl.h:1096-1099)
+    CUDA_TRY(cudaMemcpyAsync(coef, src, wq * 8, cudaMemcpyDeviceToDevice, s));
+    if (format == 0 && (rc = ring_ntt(b->from, coef, batch, true, s, "fhe_approx_mod_up"))) return rc;
+    CUDA_TRY(launch_basis_switch(b->dev, partP, sp, 0, coef, sq, 0, batch, logN, s));          // :1105-1106
+    if ((rc = ring_ntt(b->to, partP, batch, false, s, "fhe_approx_mod_up"))) return rc;        // :1113-1116
+    CUDA_TRY(copy_towers(dst, sq + sp, sq, partP, sp, 0, sp, batch, N, s));
+    if (format == 0) {
+        CUDA_TRY(copy_towers(dst, sq + sp, 0, src, sq, 0, sq, batch, N, s));                   // :1119-1123
+    } else {
+        if ((rc = ring_ntt(b->from, coef, batch, false, s, "fhe_approx_mod_up"))) return rc;   // :1124-1130
+        CUDA_TRY(copy_towers(dst, sq + sp, 0, coef, sq, 0, sq, batch, N, s));
+    }
+    return FHE_OK;
+}
+
+extern "C" int fhe_approx_mod_down(fhe_basis* b, fhe_dptr dst_q, fhe_dptr src_qp, size_t batch, uint64_t t, int stream) {
+    if (!b) return fail(FHE_EINVAL, "null basis");
+    cudaStream_t s;
+    int rc = ring_stream(b->from, stream, &s);
+    if (rc) return rc;
+    if (batch == 0) return FHE_OK;
+    if (!dst_q || !src_qp) return fail(FHE_EINVAL, "fhe_approx_mod_down: null device pointer");
+    fhe_ring *P = b->from, *Q = b->to;                      // the basis switches P -> Q
+    const uint32_t N = P->dev.N, logN = P->dev.logN, sp = b->dev.sq, sq = b->dev.sp;
+    if (!b->pinv_ready) {                                    // [P^-1]_{q_i}, rns-cryptoparameters.cpp:190-197
+        std::vector<ulonglong4> k(sq);
+        for (uint32_t i = 0; i < sq; i++) {
+            uint64_t pm = prod_mod(P->q, (size_t)-1, Q->q[i]);
+            if (pm == 0 || std::__gcd(pm, Q->q[i]) != 1) return fail(FHE_EINVAL, "fhe_approx_mod_down: P is not invertible modulo q_%u", i);
+            uint64_t c = host::invmod(pm, Q->q[i]);
+            k[i] = make_ulonglong4(c, host::shoup_companion(c, Q->q[i]), 0, 0);
+        }
+        if ((rc = upload(b->ctx, k, &b->d_pinv))) return rc;
+        b->pinv_ready = true;
+    }
+    BasisDev bd = b->dev;
+    if (t) {
+        if (b->t_cached != t) {
+            for (uint64_t pj : P->q)
+                if (std::__gcd(t % pj, pj) != 1) return fail(FHE_EINVAL, "fhe_approx_mod_down: t has no inverse modulo %llu", (unsigned long long)pj);
+            std::vector<ulonglong2> pre;
+            std::vector<BasisTarget> tgt;
+            basis_fill(b, t, pre, tgt);
+            CUDA_TRY(cudaStreamSynchronize(s));              // an earlier launch may still read the cached tables
+            if ((rc = upload(b->ctx, pre, &b->d_pre_t)) || (rc = upload(b->ctx, tgt, &b->d_tgt_t))) return rc;
+            b->t_cached = t;
+        }
+        bd.pre = (const ulonglong2*)b->d_pre_t;
+        bd.tgt = (const BasisTarget*)b->d_tgt_t;
+    }
+    uint64_t* dst = (uint64_t*)(uintptr_t)dst_q;
+    const uint64_t* src = (const uint64_t*)(uintptr_t)src_qp;
+    const size_t wq = batch * sq * (size_t)N, wp = batch * sp * (size_t)N;
+    if ((rc = b->s0.need(b->ctx, wp * 8)) || (rc = b->s1.need(b->ctx, wq * 8))) return rc;
+    uint64_t* partP = (uint64_t*)b->s0.p;
+    uint64_t* sw = (uint64_t*)b->s1.p;
+    CUDA_TRY(copy_towers(partP, sp, 0, src, sq + sp, sq, sp, batch, N, s));                    // :1150-1151
+    if ((rc = ring_ntt(P, partP, batch, true, s, "fhe_approx_mod_down"))) return rc;
+    CUDA_TRY(launch_basis_switch(bd, sw, sq, 0, partP, sp, 0, batch, logN, s));                // :1152-1159, :1170-1171
+    if ((rc = ring_ntt(Q, sw, batch, false, s, "fhe_approx_mod_down"))) return rc;             // :1172
+    CUDA_TRY(launch_tower_affine(0, dst, src, sw, batch, logN, sq, sq + sp, Q->dev.mods,       // :1173
+                                 (const ulonglong4*)b->d_pinv, s));
+    return FHE_OK;
+}
+
+struct fhe_rescale {
+    fhe_ctx* ctx = nullptr;
+    fhe_ring* ring = nullptr;
+    fhe_ring *rest = nullptr, *last = nullptr;     // views: towers [0, T-1) and [T-1, T)
+    std::vector<uint64_t> qlql, qlinv;
+    void *d_sw = nullptr, *d_k = nullptr, *d_kt = nullptr;
+    uint64_t t_cached = 0;
+    ulonglong2 pre_t{0, 0};
+    Scratch s0, s1;
+};
+
+extern "C" int fhe_rescale_destroy(fhe_rescale* p) {
+    if (!p) return FHE_OK;
+    cudaSetDevice(p->ctx->device);
+    cudaDeviceSynchronize();
+    for (void* d : {p->d_sw, p->d_k, p->d_kt})
+        if (d) p->ctx->arena.release(d);
+    p->s0.drop(p->ctx);
+    p->s1.drop(p->ctx);
+    delete p->rest;
+    delete p->last;
+    delete p;
+    return FHE_OK;
+}
+
+extern "C" int fhe_rescale_create(fhe_ring* ring, const uint64_t* qlql, const uint64_t* qlinv, fhe_rescale** out) {
+    if (!ring || !out) return fail(FHE_EINVAL, "fhe_rescale_create: null argument");
+    *out = nullptr;
+    const uint32_t T = ring->dev.T;
+    if (T < 2) return fail(FHE_EINVAL, "Removing last element of DCRTPoly object renders it invalid!");   // dcrtpoly-impl.h:722-723
+    CUDA_TRY(cudaSetDevice(ring->ctx->device));
+    auto* p = new fhe_rescale;
+    p->ctx = ring->ctx; p->ring = ring;
+    int rc;
+    if ((rc = fhe_ring_view(ring, 0, T - 1, &p->rest)) || (rc = fhe_ring_view(ring, T - 1, 1, &p->last))) {
+        fhe_rescale_destroy(p);
+        return rc;
+    }
+    const uint32_t l = T - 1;
+    const uint64_t ql = ring->q[l];
+    p->qlql.resize(l); p->qlinv.resize(l);
+    std::vector<ulonglong4> sw(l), k(l);
+    for (uint32_t i = 0; i < l; i++) {
+        const uint64_t qi = ring->q[i];
+        if (std::__gcd(ql % qi, qi) != 1) { fhe_rescale_destroy(p); return fail(FHE_EINVAL, "fhe_rescale_create: q_%u and the last modulus are not coprime", i); }
+        // Ql*[Ql^-1]_{ql} = 1 + m*ql, so floor(./ql) = m = -ql^-1 (mod q_i): q_i divides Ql
+        p->qlinv[i] = qlinv ? qlinv[i] : host::invmod(ql % qi, qi);
+        p->qlql[i] = qlql ? qlql[i] : (qi - host::invmod(ql % qi, qi)) % qi;
+        const bool up = qi > ql;                     // NativeVectorT::SwitchModulus, mubintvecnat.cpp:112-135
+        sw[i] = make_ulonglong4(ql >> 1, qi, up ? qi - ql : qi - (ql % qi), up ? 1 : 0);
+        k[i] = make_ulonglong4(p->qlql[i] % qi, host::shoup_companion(p->qlql[i] % qi, qi), 0, 0);
+    }
+    if ((rc = upload(p->ctx, sw, &p->d_sw))) { fhe_rescale_destroy(p); return rc; }
+    // k: {qlql, companion} for the spread; the affine tail wants {qlinv, companion, t, companion}
+    std::vector<ulonglong4> kk(2 * l);
+    for (uint32_t i = 0; i < l; i++) {
+        kk[i] = k[i];
+        kk[l + i] = make_ulonglong4(p->qlinv[i] % ring->q[i], host::shoup_companion(p->qlinv[i] % ring->q[i], ring->q[i]), 0, 0);
+    }
+    if ((rc = upload(p->ctx, kk, &p->d_k))) { fhe_rescale_destroy(p); return rc; }
+    *out = p;
+    return FHE_OK;
+}
+
+extern "C" int fhe_rescale_tables(const fhe_rescale* p, uint64_t* qlql, uint64_t* qlinv) {
+    if (!p) return fail(FHE_EINVAL, "null rescale plan");
+    if (qlql) memcpy(qlql, p->qlql.data(), p->qlql.size() * 8);
+    if (qlinv) memcpy(qlinv, p->qlinv.data(), p->qlinv.size() * 8);
+    return FHE_OK;
+}
+
+static int rescale_run(fhe_rescale* p, fhe_dptr dst_, fhe_dptr src_, size_t batch, uint64_t t, int format, int stream,
+                       const char* who) {
+    if (!p) return fail(FHE_EINVAL, "null rescale plan");
+    cudaStream_t s;
+    int rc = ring_stream(p->ring, stream, &s);
+    if (rc) return rc;
+    if (format != 0 && format != 1) return fail(FHE_EINVAL, "%s: format must be 0 or 1", who);
+    if (batch == 0) return FHE_OK;
+    if (!dst_ || !src_) return fail(FHE_EINVAL, "%s: null device pointer", who);
+    const uint32_t N = p->ring->dev.N, logN = p->ring->dev.logN, T = p->ring->dev.T, l = T - 1;
+    const uint64_t ql = p->ring->q[l];
+    uint64_t* dst = (uint64_t*)(uintptr_t)dst_;
+    const uint64_t* src = (const uint64_t*)(uintptr_t)src_;
+    const ulonglong4* kspread = (const ulonglong4*)p->d_k;
+    const ulonglong4* ktail = kspread + l;
+    if (t) {                                        // bgvrns-cryptoparameters.cpp:91-99
+        if (p->t_cached != t) {
+            if (std::__gcd(t % ql, ql) != 1) return fail(FHE_EINVAL, "%s: t has no inverse modulo the last modulus", who);
+            uint64_t negtinv = ql - host::invmod(t % ql, ql);
+            std::vector<ulonglong4> kt(l);
+            for (uint32_t i = 0; i < l; i++) {
+                const uint64_t qi = p->ring->q[i], c = p->qlinv[i] % qi, tt = t % qi;
+                kt[i] = make_ulonglong4(c, host::shoup_companion(c, qi), tt, host::shoup_companion(tt, qi));
+            }
+            CUDA_TRY(cudaStreamSynchronize(s));
+            if ((rc = upload(p->ctx, kt, &p->d_kt))) return rc;
+            p->pre_t = make_ulonglong2(negtinv, host::shoup_companion(negtinv, ql));
+            p->t_cached = t;
+        }
+        ktail = (const ulonglong4*)p->d_kt;
+    }
+    if ((rc = p->s0.need(p->ctx, batch * (size_t)N * 8)) || (rc = p->s1.need(p->ctx, batch * l * (size_t)N * 8))) return rc;
+    uint64_t* lastp = (uint64_t*)p->s0.p;
+    uint64_t* tmp = (uint64_t*)p->s1.p;
+    CUDA_TRY(copy_towers(lastp, 1, 0, src, T, l, 1, batch, N, s));
+    if (format == 0 && (rc = ring_ntt(p->last, lastp, batch, true, s, who))) return rc;        // SetFormat(COEFFICIENT)
+    CUDA_TRY(launch_rescale_spread(tmp, lastp, batch, logN, l, ql, (const ulonglong4*)p->d_sw, kspread, p->pre_t, t ? 1 : 0, s));
+    if (format == 0 && (rc = ring_ntt(p->rest, tmp, batch, false, s, who))) return rc;
+    CUDA_TRY(launch_tower_affine(t ? 2 : 1, dst, src, tmp, batch, logN, l, T, p->rest->dev.mods, ktail, s));
+    if (format == 1 && !t && (rc = ring_ntt(p->rest, dst, batch, false, s, who))) return rc;   // dcrtpoly-impl.h:765-766
+    return FHE_OK;
+}
+
+extern "C" int fhe_drop_last_element_and_scale(fhe_rescale* p, fhe_dptr dst, fhe_dptr src, size_t batch, int format, int stream) {
+    return rescale_run(p, dst, src, batch, 0, format, stream, "fhe_drop_last_element_and_scale");
+}
+extern "C" int fhe_mod_reduce(fhe_rescale* p, fhe_dptr dst, fhe_dptr src, size_t batch, uint64_t t, int format, int stream) {
+    if (t == 0) return fail(FHE_EINVAL, "fhe_mod_reduce: t must be positive");
+    return rescale_run(p, dst, src, batch, t, format, stream, "fhe_mod_reduce");
+}
+
+// ---------------------------------------------------------------------------------------------
 // host-operand pipelines: chunk the batch, rotate over the stream pool so that the H2D copy of
 // chunk k+1, the kernel of chunk k and the D2H copy of chunk k-1 overlap.
 // ---------------------------------------------------------------------------------------------

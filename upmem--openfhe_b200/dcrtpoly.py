@@ -287,3 +287,80 @@ class DCRTPolyBatch:
     def SetFormat(self, fmt):
         if self.format != fmt:
             self.SwitchFormat()
+
+
+# ---- RNS basis conversion and scaling -----------------------------------------
+class RingView(Ring):
+    """Towers [first, first+count) of a parent Ring, sharing its tables (fhe_ring_view)."""
+
+    def __init__(self, parent, first, count):
+        self.be, self.n, self.parent = parent.be, parent.n, parent
+        self.q = parent.q[first:first + count].copy()
+        self.psi = None if parent.psi is None else parent.psi[first:first + count].copy()
+        self.towers = count
+        h = ctypes.c_void_p()
+        N.check(N.lib.fhe_ring_view(parent.h, first, count, ctypes.byref(h)))
+        self.h = h
+
+
+class Basis:
+    """Tables of DCRTPolyImpl::ApproxSwitchCRTBasis from ring `src` to ring `dst` (dcrtpoly-impl.h:1034-1082) and
+    the two composites built on it.  Operands are raw device addresses, layouts [batch][towers][N]."""
+
+    def __init__(self, src, dst, qhat_inv_modq=None, qhat_modp=None):
+        self.src, self.dst = src, dst
+        h = ctypes.c_void_p()
+        a = None if qhat_inv_modq is None else _ptr(np.ascontiguousarray(qhat_inv_modq, np.uint64))
+        b = None if qhat_modp is None else _ptr(np.ascontiguousarray(qhat_modp, np.uint64))
+        N.check(N.lib.fhe_basis_create(src.h, dst.h, a, b, ctypes.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_basis_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        hi = np.empty(self.src.towers, np.uint64)
+        hm = np.empty((self.src.towers, self.dst.towers), np.uint64)
+        N.check(N.lib.fhe_basis_tables(self.h, _ptr(hi), _ptr(hm)))
+        return hi, hm
+
+    def approx_switch(self, dst, src, batch, stream=0):
+        N.check(N.lib.fhe_approx_switch_crt_basis(self.h, dst, src, batch, stream))
+
+    def approx_mod_up(self, dst_qp, src_q, batch, fmt, stream=0):
+        """self = Q -> P.  DCRTPolyImpl::ApproxModUp (dcrtpoly-impl.h:1085-1133)."""
+        N.check(N.lib.fhe_approx_mod_up(self.h, dst_qp, src_q, batch, fmt, stream))
+
+    def approx_mod_down(self, dst_q, src_qp, batch, t=0, stream=0):
+        """self = P -> Q.  DCRTPolyImpl::ApproxModDown (dcrtpoly-impl.h:1136-1175)."""
+        N.check(N.lib.fhe_approx_mod_down(self.h, dst_q, src_qp, batch, t, stream))
+
+
+class Rescale:
+    """DCRTPolyImpl::DropLastElementAndScale / ModReduce (dcrtpoly-impl.h:746-812) for a ring's last tower."""
+
+    def __init__(self, ring, qlql=None, qlinv=None):
+        self.ring = ring
+        h = ctypes.c_void_p()
+        a = None if qlql is None else _ptr(np.ascontiguousarray(qlql, np.uint64))
+        b = None if qlinv is None else _ptr(np.ascontiguousarray(qlinv, np.uint64))
+        N.check(N.lib.fhe_rescale_create(ring.h, a, b, ctypes.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_rescale_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        a, b = np.empty(self.ring.towers - 1, np.uint64), np.empty(self.ring.towers - 1, np.uint64)
+        N.check(N.lib.fhe_rescale_tables(self.h, _ptr(a), _ptr(b)))
+        return a, b
+
+    def drop_last_element_and_scale(self, dst, src, batch, fmt, stream=0):
+        N.check(N.lib.fhe_drop_last_element_and_scale(self.h, dst, src, batch, fmt, stream))
+
+    def mod_reduce(self, dst, src, batch, t, fmt, stream=0):
+        N.check(N.lib.fhe_mod_reduce(self.h, dst, src, batch, t, fmt, stream))
