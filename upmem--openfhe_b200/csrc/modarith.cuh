@@ -90,6 +90,40 @@ __device__ __forceinline__ u64 shoup_lazy(u64 x, u64 w, u64 wp, u64 nq) {
     return acc;
 }
 
+// The same with the quotient estimated from three of the four 32x32 partial products of x * wp (the low x low one
+// is dropped, the two middle ones contribute only their high words): the estimate is at most 2 short, so the
+// result is in [0, 4q) for any 64-bit x.  5 half-rate multiplies + 4 full-rate ones instead of 6 + 4.
+__device__ __forceinline__ u64 shoup_lazy_approx(u64 x, u64 w, u64 wp, u64 nq) {
+    u32 x0 = (u32)x, x1 = (u32)(x >> 32), w0 = (u32)w, w1 = (u32)(w >> 32);
+    u32 p0 = (u32)wp, p1 = (u32)(wp >> 32), n0 = (u32)nq, n1 = (u32)(nq >> 32);
+    u32 t1, t2;
+    asm("mul.hi.u32 %0, %1, %2;" : "=r"(t1) : "r"(x1), "r"(p0));
+    asm("mul.hi.u32 %0, %1, %2;" : "=r"(t2) : "r"(x0), "r"(p1));
+    u64 qh = (u64)t1 + (u64)t2;
+    asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(qh) : "r"(x1), "r"(p1));
+    u32 h0 = (u32)qh, h1 = (u32)(qh >> 32);
+    u64 acc;
+    u32 lo, hi;
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(acc) : "r"(x0), "r"(w0));
+    asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(h0), "r"(n0));
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(acc));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(x0), "r"(w1));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(x1), "r"(w0));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(h0), "r"(n1));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(h1), "r"(n0));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(acc) : "r"(lo), "r"(hi));
+    return acc;
+}
+
+// Butterfly multiplier of the NTT kernels: SHOUP_G = bound (in units of q) of its result.
+#ifndef FHE_NTT_EXACT_MULHI
+constexpr int SHOUP_G = 4;
+__device__ __forceinline__ u64 shoup_bf(u64 x, u64 w, u64 wp, u64 nq) { return shoup_lazy_approx(x, w, wp, nq); }
+#else
+constexpr int SHOUP_G = 2;
+__device__ __forceinline__ u64 shoup_bf(u64 x, u64 w, u64 wp, u64 nq) { return shoup_lazy(x, w, wp, nq); }
+#endif
+
 // Fully reduced Shoup product (what ModMulFastConstEq returns).
 __device__ __forceinline__ u64 shoup(u64 x, u64 w, u64 wp, u64 q) {
     return csub(shoup_lazy(x, w, wp, 0ull - q), q);
@@ -131,18 +165,19 @@ __device__ __forceinline__ u64 reduce16(u64 v, const u64* kq, u32 rsh, float rin
     return csub(v - kq[k], q);
 }
 
-// Forward (Cooley-Tukey): X in [0,Bq), Y anything below 2^64 -> both in [0,(B+2)q).  No reduction of X.
-__device__ __forceinline__ void fwd_bf(u64& X, u64& Y, u64 w, u64 wp, u64 q2, u64 nq) {
-    u64 t = shoup_lazy(Y, w, wp, nq);            // [0,2q)
-    Y = X - t + q2;
+// Forward (Cooley-Tukey): X in [0,Bq), Y anything below 2^64 -> both in [0,(B+SHOUP_G)q).  No reduction of X.
+// qg = SHOUP_G * q.
+__device__ __forceinline__ void fwd_bf(u64& X, u64& Y, u64 w, u64 wp, u64 qg, u64 nq) {
+    u64 t = shoup_bf(Y, w, wp, nq);              // [0, SHOUP_G*q)
+    Y = X - t + qg;
     X = X + t;
 }
-// Inverse (Gentleman-Sande): X in [0,BXq), Y in [0,BYq) -> X in [0,(BX+BY)q), Y in [0,2q).
+// Inverse (Gentleman-Sande): X in [0,BXq), Y in [0,BYq) -> X in [0,(BX+BY)q), Y in [0,SHOUP_G*q).
 // byq = BY*q keeps the difference non-negative.
 __device__ __forceinline__ void inv_bf(u64& X, u64& Y, u64 w, u64 wp, u64 byq, u64 nq) {
     u64 d = X - Y + byq;
     X = X + Y;
-    Y = shoup_lazy(d, w, wp, nq);
+    Y = shoup_bf(d, w, wp, nq);
 }
 
 }  // namespace fhe

@@ -15,8 +15,9 @@
 //   contig pass : 256-point sub-NTTs over contiguous blocks (stages L-8..L-1); a tile takes the
 //                 SAME block of up to 16 different batch items so twiddle loads are shared.
 // Each thread keeps 16 coefficients in registers and runs 4 butterfly stages per step (radix-16),
-// one shared-memory exchange per pass.  Harvey lazy reduction: forward values live in [0,4q),
-// inverse values in [0,2q); the last store of a transform reduces to [0,q).
+// one shared-memory exchange per pass.  Lazy reduction with compile-time range tracking: values stay below 16q
+// (q < 2^60) and the butterfly multiplier returns [0,4q) (quotient estimated from three of the four partial
+// products, modarith.cuh); the last store of a transform reduces to [0,q), so outputs equal the reference's.
 // HBM traffic: 32 B per coefficient per transform (two passes); twiddles amortised over the batch.
 // N <= 256 (and any N <= 4096 on request) uses one CTA per tower entirely in shared memory.
 #include "modarith.cuh"
@@ -42,27 +43,38 @@ constexpr int MAXB = 16;
 constexpr int INV_NORM = 4;  // uniform bound the inverse restores between register steps and between the two passes     // values stay below MAXB*q < 2^64 (q < 2^60)
 
 // ---- forward: E = bound (in units of q) of every coefficient entering a step of S stages.
-// A stage adds 2 to the bound of both outputs whatever the bound of the multiplied input, so only the
-// elements that are NOT multiplied in the first stage have to be pulled below 16 - 2S on entry.
+// A stage adds SHOUP_G to the bound of both outputs whatever the bound of the multiplied input, so only the
+// elements that are NOT multiplied in a stage have to be below 16 - SHOUP_G when it starts; where the running
+// bound would pass that, those elements take one conditional subtraction of 8q first.  Simulated at compile time.
 template <int S, int E>
 struct FwdStep {
-    static constexpr int LIM = MAXB - 2 * S;
-    static constexpr int XB  = E > LIM ? 8 : E;          // after one conditional subtraction of 8q
-    static constexpr int OUT = XB + 2 * S;
+    static constexpr int before(int j) {                 // bound entering stage j, before its optional reduction
+        int b = E;
+        for (int k = 0; k < j; k++) {
+            if (b + SHOUP_G > MAXB) b = 8;
+            b += SHOUP_G;
+        }
+        return b;
+    }
+    static constexpr bool reduce(int j) { return before(j) + SHOUP_G > MAXB; }
+    static constexpr int OUT = before(S);
     static_assert(E <= MAXB && OUT <= MAXB, "forward step overflows the 16q headroom");
 };
 
 // One butterfly stage J (of S) on 2^S register-resident coefficients.  The coefficients are the
 // sub-NTT whose twiddle prefix is P: stage J uses table[(P << J) + (e >> (S-J))].
-template <int S, int J>
+template <int S, int J, bool REDUCE>
 __device__ __forceinline__ void fwd_stage(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw, u32 P,
-                                          u64 q2, u64 nq) {
+                                          u64 qg, u64 q8, u64 nq) {
     constexpr int half = 1 << (S - 1 - J);
 #pragma unroll
     for (int g = 0; g < (1 << J); g++) {
         ulonglong2 w = ldtw(tw + ((P << J) + g));
 #pragma unroll
-        for (int i = 0; i < half; i++) fwd_bf(x[g * 2 * half + i], x[g * 2 * half + i + half], w.x, w.y, q2, nq);
+        for (int i = 0; i < half; i++) {
+            if constexpr (REDUCE) x[g * 2 * half + i] = csub(x[g * 2 * half + i], q8);
+            fwd_bf(x[g * 2 * half + i], x[g * 2 * half + i + half], w.x, w.y, qg, nq);
+        }
     }
 }
 
@@ -70,11 +82,10 @@ template <int S, int E>
 __device__ __forceinline__ void fwd_step(u64 (&x)[1 << S], const ulonglong2* __restrict__ tw, u32 P,
                                          const QMul& Q, u64 nq) {
     if constexpr (S > 0) {
-        if constexpr (E > FwdStep<S, E>::LIM) {
-#pragma unroll
-            for (int e = 0; e < (1 << (S - 1)); e++) x[e] = csub(x[e], Q.q8);
-        }
-        static_for<0, S>([&](auto j) { fwd_stage<S, decltype(j)::value>(x, tw, P, Q.q2, nq); });
+        static_for<0, S>([&](auto j) {
+            constexpr int J = decltype(j)::value;
+            fwd_stage<S, J, FwdStep<S, E>::reduce(J)>(x, tw, P, qm<SHOUP_G>(Q), Q.q8, nq);
+        });
     }
 }
 
@@ -102,7 +113,7 @@ constexpr InvPlan<S> make_inv_plan(int E, int NORM) {
                 if (bx >= by) bx = bx > 8 ? 8 : bx / 2; else by = by > 8 ? 8 : by / 2;
             }
             p.tgt[k][e] = bx; p.tgt[k][e + half] = by;
-            b[e] = bx + by; b[e + half] = 2;
+            b[e] = bx + by; b[e + half] = SHOUP_G;
         }
     }
     for (int e = 0; e < (1 << S); e++) {
