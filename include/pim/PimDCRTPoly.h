@@ -11,6 +11,8 @@
  *   operator+= -= *= (no checks)    dcrtpoly-impl.h:410-416, 438-444, dcrtpoly.h:142-148
  *   SwitchFormat / SetFormat        dcrtpoly-impl.h:2518-2524, lattice/ilelement.h:448-451
  *   AutomorphismTransform           dcrtpoly-impl.h:348-369, poly-impl.h:312-380
+ *   ApproxSwitchCRTBasis / ApproxModUp / ApproxModDown      dcrtpoly-impl.h:1034-1175
+ *   DropLastElementAndScale / ModReduce                     dcrtpoly-impl.h:746-812
  * Layout in HBM: [batch][tower][N] uint64.  Header only; link with libfhe_b200.so.
  */
 #ifndef _PIM_DCRT_POLY_
@@ -38,6 +40,11 @@ public:
     PimManager::check(fhe_ring_create(pim->context(), N, (uint32_t)q.size(), q_.data(),
                                       psi_.empty() ? nullptr : psi_.data(), &ring_), "PimRing");
   }
+  /* towers [first, first+count) of `parent`, sharing its device tables (the ILDCRTParams of a sub-basis) */
+  static std::shared_ptr<PimRing> View(const std::shared_ptr<PimRing> &parent, uint32_t first, uint32_t count) {
+    std::shared_ptr<PimRing> v(new PimRing(parent, first, count));
+    return v;
+  }
   ~PimRing() { fhe_ring_destroy(ring_); }
   PimRing(const PimRing &) = delete;
   PimRing &operator=(const PimRing &) = delete;
@@ -57,10 +64,61 @@ public:
   PimManager *manager() const { return pim_; }
 
 private:
+  PimRing(const std::shared_ptr<PimRing> &parent, uint32_t first, uint32_t count)
+      : pim_(parent->pim_), n_(parent->n_), parent_(parent) {
+    PimManager::check(fhe_ring_view(parent->ring_, first, count, &ring_), "PimRing::View");
+    q_.assign(parent->q_.begin() + first, parent->q_.begin() + first + count);
+    if (!parent->psi_.empty()) psi_.assign(parent->psi_.begin() + first, parent->psi_.begin() + first + count);
+  }
   PimManager *pim_;
   uint32_t n_;
   std::vector<uint64_t> q_, psi_;
   fhe_ring *ring_ = nullptr;
+  std::shared_ptr<PimRing> parent_;   /* keeps the owner of the tables alive */
+};
+
+/* Tables of DCRTPolyImpl::ApproxSwitchCRTBasis from one basis to another (dcrtpoly-impl.h:1034-1082): what
+ * CryptoParametersRNS precomputes per basis pair (rns-cryptoparameters.cpp:190-229, 273-283).  Pass the
+ * scheme's own QHatInvModq / QHatModp, or leave them empty to have them derived from the moduli. */
+class PimBasis {
+public:
+  PimBasis(std::shared_ptr<PimRing> from, std::shared_ptr<PimRing> to, const std::vector<uint64_t> &QHatInvModq = {},
+           const std::vector<uint64_t> &QHatModp = {})
+      : from_(std::move(from)), to_(std::move(to)) {
+    PimManager::check(fhe_basis_create(from_->handle(), to_->handle(), QHatInvModq.empty() ? nullptr : QHatInvModq.data(),
+                                       QHatModp.empty() ? nullptr : QHatModp.data(), &basis_), "PimBasis");
+  }
+  ~PimBasis() { fhe_basis_destroy(basis_); }
+  PimBasis(const PimBasis &) = delete;
+  PimBasis &operator=(const PimBasis &) = delete;
+  fhe_basis *handle() const { return basis_; }
+  const std::shared_ptr<PimRing> &From() const { return from_; }
+  const std::shared_ptr<PimRing> &To() const { return to_; }
+
+private:
+  std::shared_ptr<PimRing> from_, to_;
+  fhe_basis *basis_ = nullptr;
+};
+
+/* Constants of DropLastElementAndScale / ModReduce for a ring's last tower (ckksrns-cryptoparameters.cpp:66-88) */
+class PimRescale {
+public:
+  explicit PimRescale(std::shared_ptr<PimRing> ring, const std::vector<uint64_t> &QlQlInvModqlDivqlModq = {},
+                      const std::vector<uint64_t> &qlInvModq = {})
+      : ring_(std::move(ring)), rest_(PimRing::View(ring_, 0, (uint32_t)ring_->GetNumTowers() - 1)) {
+    PimManager::check(fhe_rescale_create(ring_->handle(), QlQlInvModqlDivqlModq.empty() ? nullptr : QlQlInvModqlDivqlModq.data(),
+                                         qlInvModq.empty() ? nullptr : qlInvModq.data(), &plan_), "PimRescale");
+  }
+  ~PimRescale() { fhe_rescale_destroy(plan_); }
+  PimRescale(const PimRescale &) = delete;
+  PimRescale &operator=(const PimRescale &) = delete;
+  fhe_rescale *handle() const { return plan_; }
+  const std::shared_ptr<PimRing> &Ring() const { return ring_; }
+  const std::shared_ptr<PimRing> &Rest() const { return rest_; }   /* params after DropLastElement */
+
+private:
+  std::shared_ptr<PimRing> ring_, rest_;
+  fhe_rescale *plan_ = nullptr;
 };
 
 class PimDCRTPoly {
@@ -136,6 +194,41 @@ public:
     return out;
   }
   void SetFormat(PimFormat f) { if (format_ != f) SwitchFormat(); }
+
+  /* dcrtpoly-impl.h:1034-1082: this over basis.From() -> result over basis.To(), same format flag */
+  PimDCRTPoly ApproxSwitchCRTBasis(const PimBasis &basis) const {
+    PimDCRTPoly out(basis.To(), batch_, format_, nullptr, stream_);
+    PimManager::check(fhe_approx_switch_crt_basis(basis.handle(), out.d_, d_, batch_, stream_), "ApproxSwitchCRTBasis");
+    return out;
+  }
+  /* dcrtpoly-impl.h:1085-1133 (the reference works in place; here the extended polynomial is returned): this over Q,
+   * qToP from Q to P, ringQP the ring of Q followed by P.  Result in EVALUATION. */
+  PimDCRTPoly ApproxModUp(const PimBasis &qToP, const std::shared_ptr<PimRing> &ringQP) const {
+    PimDCRTPoly out(ringQP, batch_, PIM_EVALUATION, nullptr, stream_);
+    PimManager::check(fhe_approx_mod_up(qToP.handle(), out.d_, d_, batch_, (int)format_, stream_), "ApproxModUp");
+    return out;
+  }
+  /* dcrtpoly-impl.h:1136-1175: this over QP in EVALUATION, pToQ from P to Q; t > 0 selects the BGV form */
+  PimDCRTPoly ApproxModDown(const PimBasis &pToQ, uint64_t t = 0) const {
+    if (format_ != PIM_EVALUATION) throw pim_not_implemented_error("ApproxModDown expects Format::EVALUATION");
+    PimDCRTPoly out(pToQ.To(), batch_, PIM_EVALUATION, nullptr, stream_);
+    PimManager::check(fhe_approx_mod_down(pToQ.handle(), out.d_, d_, batch_, t, stream_), "ApproxModDown");
+    return out;
+  }
+  /* dcrtpoly-impl.h:746-769 (in place in the reference).  As there, a COEFFICIENT input comes back with forward-
+   * transformed towers while the format flag stays COEFFICIENT (dcrtpoly-impl.h:765-766). */
+  PimDCRTPoly DropLastElementAndScale(const PimRescale &plan) const {
+    PimDCRTPoly out(plan.Rest(), batch_, format_, nullptr, stream_);
+    PimManager::check(fhe_drop_last_element_and_scale(plan.handle(), out.d_, d_, batch_, (int)format_, stream_),
+                      "DropLastElementAndScale");
+    return out;
+  }
+  /* dcrtpoly-impl.h:792-812 */
+  PimDCRTPoly ModReduce(const PimRescale &plan, uint64_t t) const {
+    PimDCRTPoly out(plan.Rest(), batch_, format_, nullptr, stream_);
+    PimManager::check(fhe_mod_reduce(plan.handle(), out.d_, d_, batch_, t, (int)format_, stream_), "ModReduce");
+    return out;
+  }
 
 private:
   fhe_ctx *ctx() const { return ring_->manager()->context(); }

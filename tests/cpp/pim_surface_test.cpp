@@ -140,6 +140,52 @@ static void test_dcrtpoly(uint32_t N, uint32_t T, size_t B) {
     orc_ctx_destroy(oc);
 }
 
+// SURVEY §8(f) ranks 3 and 4 through the C++ surface
+static void test_dcrtpoly_ext(uint32_t N, uint32_t sq, uint32_t sp, size_t B) {
+    PimManager* pim = PimManager::getPim(4);
+    uint32_t T = sq + sp;
+    auto ring = PimRing::Generate(pim, 60, N, T);
+    auto ringQ = PimRing::View(ring, 0, sq), ringP = PimRing::View(ring, sq, sp);
+    const auto &q = ring->GetModuli(), &psi = ring->GetRoots();
+    orc_ctx *oQP = orc_ctx_create(N, T, q.data(), psi.data()), *oQ = orc_ctx_create(N, sq, q.data(), psi.data()),
+            *oP = orc_ctx_create(N, sp, q.data() + sq, psi.data() + sq), *oR = orc_ctx_create(N, T - 1, q.data(), psi.data()),
+            *oL = orc_ctx_create(N, 1, q.data() + T - 1, psi.data() + T - 1);
+    std::vector<uint64_t> hx(B * sq * (size_t)N), hy(B * T * (size_t)N);
+    for (size_t u = 0; u < B * sq; u++) orc_fill_uniform(&hx[u * N], N, q[u % sq], 7, u * (size_t)N);
+    for (size_t u = 0; u < B * T; u++) orc_fill_uniform(&hy[u * N], N, q[u % T], 8, u * (size_t)N);
+    PimDCRTPoly x(ringQ, B, PIM_EVALUATION, hx.data()), y(ring, B, PIM_EVALUATION, hy.data());
+
+    std::vector<uint64_t> exp(hy.size());
+    orc_dcrt_automorphism(oQP, exp.data(), hy.data(), B, 5, 0);
+    EXPECT(y.AutomorphismTransform(5).GetValues() == exp, "AutomorphismTransform N=%u", N);
+    bool threw = false;
+    try { y.AutomorphismTransform(6); } catch (const pim_math_error&) { threw = true; }
+    EXPECT(threw, "even automorphism index must throw");
+
+    PimBasis qToP(ringQ, ringP), pToQ(ringP, ringQ);
+    orc_approx_mod_up(oQ, oP, exp.data(), hx.data(), B, 0);
+    PimDCRTPoly up = x.ApproxModUp(qToP, ring);
+    EXPECT(up.GetFormat() == PIM_EVALUATION && up.GetValues() == exp, "ApproxModUp N=%u", N);
+    for (uint64_t t : {0ull, 65537ull}) {
+        std::vector<uint64_t> e2(B * sq * (size_t)N);
+        orc_approx_mod_down(oQ, oP, e2.data(), hy.data(), B, t);
+        EXPECT(y.ApproxModDown(pToQ, t).GetValues() == e2, "ApproxModDown t=%llu N=%u", (unsigned long long)t, N);
+        std::vector<uint64_t> e3(B * (T - 1) * (size_t)N);
+        orc_rescale(oQP, oR, oL, e3.data(), hy.data(), B, 0, t);
+        PimRescale plan(ring);
+        PimDCRTPoly r = t ? y.ModReduce(plan, t) : y.DropLastElementAndScale(plan);
+        EXPECT(r.GetParams()->GetNumTowers() == T - 1 && r.GetValues() == e3, "rescale t=%llu N=%u", (unsigned long long)t, N);
+    }
+    PimDCRTPoly xc(x);
+    xc.SetFormat(PIM_COEFFICIENT);
+    std::vector<uint64_t> hi(sq), hm((size_t)sq * sp), e4(B * sp * (size_t)N), coef(hx);
+    orc_dcrt_ntt(oQ, 1, coef.data(), B, 0);
+    orc_switch_tables(q.data(), sq, q.data() + sq, sp, hi.data(), hm.data());
+    orc_approx_switch(e4.data(), coef.data(), B, N, q.data(), sq, q.data() + sq, sp, hi.data(), hm.data());
+    EXPECT(xc.ApproxSwitchCRTBasis(qToP).GetValues() == e4, "ApproxSwitchCRTBasis N=%u", N);
+    for (orc_ctx* c : {oQP, oQ, oP, oR, oL}) orc_ctx_destroy(c);
+}
+
 int main() {
     try {
         test_pimdata_kat();
@@ -151,6 +197,8 @@ int main() {
         test_dcrtpoly(1 << 14, 2, 2);      // BASELINE configs[0]
         test_dcrtpoly(1 << 16, 3, 2);
         test_dcrtpoly(1 << 11, 4, 3);
+        test_dcrtpoly_ext(1 << 12, 3, 2, 2);
+        test_dcrtpoly_ext(1 << 14, 5, 3, 1);
     } catch (const std::exception& e) {
         printf("FAIL exception: %s\n", e.what());
         failures++;
