@@ -9,9 +9,10 @@
  * is oracle/hook_patch.py (applied to a temporary copy of the reference headers).
  *
  * The templates are duck-typed on OpenFHE's PolyImpl<NativeVector> (GetValues, GetModulus,
- * GetRootOfUnity, GetRingDimension, SetValues) so this header needs no OpenFHE include.  This is the
- * copy-per-call form of the hook (operands live in host memory between calls, like the fork's);
- * PimDCRTPoly.h is the resident form.  Failures throw: there is no silent CPU fallback.
+ * GetRootOfUnity, GetRingDimension, SetValues) so this header needs no OpenFHE include.  Two forms:
+ * copy-per-call (dcrt_eq / dcrt_switch_format: operands live in host memory between calls, like the fork's; needs
+ * no change to the class layout) and resident (Resident / resident_eq / resident_switch_format below: the towers
+ * stay in HBM between hooked operators).  Failures throw: there is no silent CPU fallback.
  */
 #ifndef _PIM_HOOK_
 #define _PIM_HOOK_
@@ -103,6 +104,87 @@ inline bool dcrt_switch_format(PimManager *pim, Towers &a, bool to_evaluation, F
     PimManager::check(fhe_sync(ctx, 0), "pim hook: sync");
     a[t].SetValues(std::move(v), new_format);       /* sets the tower's format without transforming on the CPU */
   }
+  return true;
+}
+
+/* ---- resident form ---------------------------------------------------------------------------------------
+ * A DCRTPolyImpl that has been through a hooked operator keeps its towers in HBM ([T][N] words) and only the
+ * device copy is updated by further hooked operators; the host towers are refreshed lazily, the first time
+ * anything else reads them.  oracle/hook_patch.py arranges that by renaming the member to m_vectors_ and routing
+ * every other use of `m_vectors` through DCRTPolyImpl::PimHostVectors() (const: download if the device copy is
+ * newer; non-const: download, then drop the device copy because the caller may write).  This is the
+ * "operands stay resident between ops; host copies only on sync()" intent of pim/PimData.h:16-34 applied at
+ * DCRTPoly level. */
+struct Resident {
+  std::shared_ptr<PimRing> ring;
+  fhe_ctx *ctx = nullptr;
+  fhe_dptr d = 0;
+  size_t towers = 0, n = 0;
+  bool device_newer = false;          /* guarded by mu */
+  std::mutex mu;
+  ~Resident() { if (d) fhe_free(ctx, d); }
+};
+
+inline long &resident_uploads() { static long n = 0; return n; }     /* counters for the tests */
+inline long &resident_downloads() { static long n = 0; return n; }
+
+/* makes `towers` resident (uploading them if they are not yet) and returns the device copy */
+template <class Towers>
+inline std::shared_ptr<Resident> ensure_device(PimManager *pim, const Towers &towers, std::shared_ptr<Resident> &res) {
+  if (res && res->towers == towers.size() && res->n == towers[0].GetRingDimension()) return res;
+  auto r = std::make_shared<Resident>();
+  r->ring = ring_of(pim, towers);
+  r->ctx = pim->context();
+  r->towers = towers.size();
+  r->n = towers[0].GetRingDimension();
+  const size_t bytes = r->n * sizeof(uint64_t);
+  PimManager::check(fhe_alloc(r->ctx, r->towers * bytes, &r->d), "pim hook: device buffer");
+  for (size_t t = 0; t < r->towers; t++)
+    PimManager::check(fhe_h2d(r->ctx, r->d + t * bytes, words(towers[t].GetValues()), bytes, 0), "pim hook: upload");
+  PimManager::check(fhe_sync(r->ctx, 0), "pim hook: sync");     /* the host towers may change after this call */
+  resident_uploads()++;
+  res = r;
+  return r;
+}
+
+/* host towers <- device copy if that is newer; every tower is put in `format` (the DCRTPoly's own) */
+template <class Towers, class Format>
+inline void sync_host(Towers &towers, const std::shared_ptr<Resident> &res, Format format) {
+  if (!res) return;
+  std::lock_guard<std::mutex> lock(res->mu);
+  if (!res->device_newer) return;
+  const size_t bytes = res->n * sizeof(uint64_t);
+  for (size_t t = 0; t < res->towers; t++) {
+    auto v = towers[t].GetValues();
+    PimManager::check(fhe_d2h(res->ctx, const_cast<uint64_t *>(words(v)), res->d + t * bytes, bytes, 0), "pim hook: download");
+    PimManager::check(fhe_sync(res->ctx, 0), "pim hook: sync");
+    towers[t].SetValues(std::move(v), format);
+  }
+  resident_downloads()++;
+  res->device_newer = false;
+}
+
+/* a (op)= b on the device copies; nothing crosses PCIe when both are already resident */
+template <class Towers>
+inline bool resident_eq(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &b,
+                        std::shared_ptr<Resident> &rb, int op) {
+  if (!pim || a.empty() || a.size() != b.size()) return false;
+  auto da = ensure_device(pim, a, ra);
+  auto db = (&a == &b) ? da : ensure_device(pim, b, rb);
+  PimManager::check(fhe_dcrt_op(da->ring->handle(), op, da->d, da->d, db->d, 1, 0), "pim hook: dcrt op");
+  std::lock_guard<std::mutex> lock(da->mu);
+  da->device_newer = true;
+  return true;
+}
+
+template <class Towers>
+inline bool resident_switch_format(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, bool to_evaluation) {
+  if (!pim || a.empty()) return false;
+  auto da = ensure_device(pim, a, ra);
+  PimManager::check(to_evaluation ? fhe_ntt_forward(da->ring->handle(), da->d, 1, 0) : fhe_ntt_inverse(da->ring->handle(), da->d, 1, 0),
+                    "pim hook: transform");
+  std::lock_guard<std::mutex> lock(da->mu);
+  da->device_newer = true;
   return true;
 }
 

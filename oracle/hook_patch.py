@@ -11,7 +11,11 @@ sources are never copied into the repo) and applies the few-line patch INTEGRATI
   2. remove the `PimData pim_m_data = {1,2,3,4};` member every NativeVector carries (mubintvecnat.h:128),
      which would allocate device memory per vector;
   3. insert the intercept calls (pim/PimHook.h) at the top of DCRTPolyImpl::operator+= / -= / *= and
-     SwitchFormat (dcrtpoly-impl.h:410-416, 438-444, 2518-2524; dcrtpoly.h:142-148).
+     SwitchFormat (dcrtpoly-impl.h:410-416, 438-444, 2518-2524; dcrtpoly.h:142-148);
+  4. resident form: rename DCRTPolyImpl's tower member to m_vectors_ (dcrtpoly.h:421), add a device copy handle
+     next to it, and route every other use of `m_vectors` in dcrtpoly.h / dcrtpoly-impl.h through the accessor
+     PimHostVectors() (a #define scoped to those two headers), which refreshes the host towers from the device
+     copy when that is newer.  Hooked operators then leave their result in HBM.
 
 Only the inserted lines are ours; anchors are matched on the reference's function signatures.
 """
@@ -44,22 +48,78 @@ def patch(rel, edits):
 
 patch("math/hal/intnat/mubintvecnat.h", [("PimData pim_m_data", "", "delete_line")])
 
-HOOK_EQ = "\n    if (pim && pimhook::dcrt_eq(pim.get(), m_vectors, rhs.m_vectors, %s))\n        return *this;"
-patch("lattice/hal/default/dcrtpoly.h", [
-    ('#include "utils/parallel.h"\n', '#include "pim/PimHook.h"\n', "after"),
-    ("DCRTPolyType& operator*=(const DCRTPolyType& rhs) override {", HOOK_EQ % "FHE_OP_MUL", "after"),
-])
-patch("lattice/hal/default/dcrtpoly-impl.h", [
-    ("DCRTPolyImpl<VecType>& DCRTPolyImpl<VecType>::operator+=(const DCRTPolyImpl& rhs) {", HOOK_EQ % "FHE_OP_ADD", "after"),
-    ("DCRTPolyImpl<VecType>& DCRTPolyImpl<VecType>::operator-=(const DCRTPolyImpl& rhs) {", HOOK_EQ % "FHE_OP_SUB", "after"),
-    ("void DCRTPolyImpl<VecType>::SwitchFormat() {",
-     "\n    if (pim) {\n"
-     "        const bool toEval = (m_format == Format::COEFFICIENT);\n"
-     "        const Format nf   = toEval ? Format::EVALUATION : Format::COEFFICIENT;\n"
-     "        if (pimhook::dcrt_switch_format(pim.get(), m_vectors, toEval, nf)) {\n"
-     "            m_format = nf;\n"
-     "            return;\n"
-     "        }\n"
-     "    }", "after"),
-])
+# ---- resident form: the member is renamed, every other use of `m_vectors` goes through an accessor ----------
+ACCESSORS = """
+    /* B200 intercept, resident form (pim/PimHook.h): host view of the towers.  const: refresh from the device copy
+     * if that is newer.  non-const: refresh, then drop the device copy (the caller may write). */
+    const std::vector<PolyType>& PimHostVectors() const {
+        if (pimres_) pimhook::sync_host(m_vectors_, pimres_, m_format);
+        return m_vectors_;
+    }
+    std::vector<PolyType>& PimHostVectors() {
+        if (pimres_) {
+            pimhook::sync_host(m_vectors_, pimres_, m_format);
+            pimres_.reset();
+        }
+        return m_vectors_;
+    }
+    mutable std::vector<PolyType> m_vectors_;
+    mutable std::shared_ptr<pimhook::Resident> pimres_;
+"""
+HOOK_EQ = ("\n    if (pim && pimhook::resident_eq(pim.get(), m_vectors_, pimres_, rhs.m_vectors_, rhs.pimres_, %s))"
+           "\n        return *this;")
+
+
+def rewrite(rel, fn):
+    path = os.path.join(out, rel)
+    text = fn(open(path).read())
+    open(path, "w").write(text)
+
+
+def once(text, old, new, rel):
+    if text.count(old) != 1:
+        raise SystemExit(f"hook_patch: anchor not found exactly once in {rel}: {old!r}")
+    return text.replace(old, new)
+
+
+def patch_class(text):
+    rel = "dcrtpoly.h"
+    text = once(text, '#include "utils/parallel.h"\n', '#include "utils/parallel.h"\n#include "pim/PimHook.h"\n', rel)
+    text = once(text, "    std::vector<PolyType> m_vectors;\n", ACCESSORS, rel)
+    text = once(text, "m_vectors{e.m_vectors} {}", "m_vectors_{e.PimHostVectors()} {}", rel)
+    text = once(text, "m_vectors{std::move(e.m_vectors)} {}",
+                "m_vectors_{std::move(e.m_vectors_)}, pimres_{std::move(e.pimres_)} {}", rel)
+    # move assignment: take the device copy along instead of forcing a download
+    text = once(text, "        m_vectors = std::move(rhs.m_vectors);\n",
+                "        m_vectors_ = std::move(rhs.m_vectors_);\n        pimres_    = std::move(rhs.pimres_);\n", rel)
+    text = once(text, "DCRTPolyType& operator*=(const DCRTPolyType& rhs) override {",
+                "DCRTPolyType& operator*=(const DCRTPolyType& rhs) override {" + HOOK_EQ % "FHE_OP_MUL", rel)
+    # everything else in this header reads the towers through the accessor
+    head, sep, tail = text.partition("namespace lbcrypto {")
+    return head + "#define m_vectors PimHostVectors()\n" + sep + tail + "\n#undef m_vectors\n"
+
+
+def patch_impl(text):
+    rel = "dcrtpoly-impl.h"
+    text = once(text, "m_vectors(params->GetParams().size(), rhs) {", "m_vectors_(params->GetParams().size(), rhs) {", rel)
+    text = once(text, "m_vectors(towers) {", "m_vectors_(towers) {", rel)
+    text = once(text, "DCRTPolyImpl<VecType>& DCRTPolyImpl<VecType>::operator+=(const DCRTPolyImpl& rhs) {",
+                "DCRTPolyImpl<VecType>& DCRTPolyImpl<VecType>::operator+=(const DCRTPolyImpl& rhs) {" + HOOK_EQ % "FHE_OP_ADD", rel)
+    text = once(text, "DCRTPolyImpl<VecType>& DCRTPolyImpl<VecType>::operator-=(const DCRTPolyImpl& rhs) {",
+                "DCRTPolyImpl<VecType>& DCRTPolyImpl<VecType>::operator-=(const DCRTPolyImpl& rhs) {" + HOOK_EQ % "FHE_OP_SUB", rel)
+    text = once(text, "void DCRTPolyImpl<VecType>::SwitchFormat() {",
+                "void DCRTPolyImpl<VecType>::SwitchFormat() {"
+                "\n    if (pim) {\n"
+                "        const bool toEval = (m_format == Format::COEFFICIENT);\n"
+                "        if (pimhook::resident_switch_format(pim.get(), m_vectors_, pimres_, toEval)) {\n"
+                "            m_format = toEval ? Format::EVALUATION : Format::COEFFICIENT;\n"
+                "            return;\n"
+                "        }\n"
+                "    }", rel)
+    head, sep, tail = text.partition("namespace lbcrypto {")
+    return head + "#define m_vectors PimHostVectors()\n" + sep + tail + "\n#undef m_vectors\n"
+
+
+rewrite("lattice/hal/default/dcrtpoly.h", patch_class)
+rewrite("lattice/hal/default/dcrtpoly-impl.h", patch_impl)
 print("hook_patch: patched header tree in", out)

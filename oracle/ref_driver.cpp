@@ -68,6 +68,16 @@ int ref_polys_set_pim(ref_polys* p, int on) {
 #endif
 }
 
+// resident-form counters of the hooked build: uploads / downloads of whole DCRTPolys so far (-1 without a hook)
+void ref_hook_counters(long* uploads, long* downloads) {
+#ifdef FHE_HOOKED
+    *uploads = pimhook::resident_uploads();
+    *downloads = pimhook::resident_downloads();
+#else
+    *uploads = *downloads = -1;
+#endif
+}
+
 // poly-benchmark-16k.cpp:82-101
 void ref_gen_params(uint32_t nbits, uint32_t N, uint32_t T, uint64_t* q, uint64_t* psi) {
     uint32_t m = 2 * N;

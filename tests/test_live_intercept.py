@@ -33,7 +33,17 @@ def hooked():
     H.ref_polys_set_pim.argtypes = [vp, ci]
     H.ref_polys_format.argtypes = [vp]
     H.ref_last_error.restype = ctypes.c_char_p
+    H.ref_hook_counters.argtypes = [vp, vp]
+    H.ref_polys_automorphism.restype = vp
+    H.ref_polys_automorphism.argtypes = [vp, u32, ci]
+    H.ref_polys_rescale.argtypes = [vp, vp, u64]
     return H
+
+
+def counters(H):
+    up, down = ctypes.c_long(), ctypes.c_long()
+    H.ref_hook_counters(ctypes.byref(up), ctypes.byref(down))
+    return up.value, down.value
 
 
 def p(a):
@@ -105,3 +115,55 @@ def test_live_intercept_matches_cpu_path(hooked, oracle, pkg, n, towers, batch):
     before = pkg._native.lib.fhe_launch_count()
     run_ops(hooked, oracle, n, towers, batch, pim_on=True)
     assert pkg._native.lib.fhe_launch_count() > before, "the intercept did not launch any kernel"
+
+
+@pytest.mark.gpu
+def test_resident_form_keeps_towers_on_the_device(hooked, oracle, pkg):
+    """Resident form of the intercept (pim/PimHook.h, oracle/hook_patch.py step 4): a chain of hooked operators on the
+    reference's own DCRTPoly uploads each operand once and downloads the result once, when something else reads it;
+    CPU-only methods called in between see the current values."""
+    H = hooked
+    n, towers, batch = 1 << 12, 4, 3
+    q, psi = oracle.gen_params(60, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    a = oracle.fill_ring(batch, n, q, 41)
+    b = oracle.fill_ring(batch, n, q, 42)
+    ctx = H.ref_ctx_create(n, towers, p(q), p(psi))
+    ha, hb = H.ref_polys_load(ctx, p(a), batch, 0), H.ref_polys_load(ctx, p(b), batch, 0)
+    assert H.ref_polys_set_pim(ha, 1) == 0, H.ref_last_error()
+    up0, down0 = counters(H)
+    launches0 = pkg._native.lib.fhe_launch_count()
+    assert H.ref_polys_op(ha, hb, 0, 1) >= 0, H.ref_last_error()        # a += b
+    assert H.ref_polys_op(ha, hb, 2, 1) >= 0                            # a *= b
+    assert H.ref_polys_switch_format(ha, 1) >= 0                        # -> COEFFICIENT
+    assert H.ref_polys_switch_format(ha, 1) >= 0                        # -> EVALUATION
+    assert H.ref_polys_op(ha, hb, 1, 1) >= 0                            # a -= b
+    up1, down1 = counters(H)
+    assert (up1 - up0, down1 - down0) == (2 * batch, 0), "operands must be uploaded once and nothing downloaded yet"
+    assert pkg._native.lib.fhe_launch_count() - launches0 >= 5 * batch
+    want = octx.elementwise(1, octx.elementwise(2, octx.elementwise(0, a, b), b), b)
+    res = np.empty_like(a)
+    H.ref_polys_store(ha, p(res))                                       # const access: lazy download
+    assert np.array_equal(res, want)
+    up2, down2 = counters(H)
+    assert (up2 - up1, down2 - down1) == (0, batch)
+    H.ref_polys_store(ha, p(res))                                       # host copy is current now
+    assert counters(H) == (up2, down2)
+    assert H.ref_polys_op(ha, hb, 0, 1) >= 0                            # device copy was still valid: no new upload
+    assert counters(H)[0] == up2
+    want = octx.elementwise(0, want, b)
+    # a CPU-only const method of the reference (AutomorphismTransform) sees the device result
+    hr = H.ref_polys_automorphism(ha, 5, 0)
+    assert hr, H.ref_last_error()
+    res2 = np.empty_like(a)
+    H.ref_polys_store(hr, p(res2))
+    assert np.array_equal(res2, octx.automorphism(want, 5, 0))
+    H.ref_polys_free(hr)
+    # a CPU-only mutating method (DropLastElementAndScale) takes the current values and invalidates the device copy
+    rest = H.ref_ctx_create(n, towers - 1, p(q[:-1].copy()), p(psi[:-1].copy()))
+    assert H.ref_polys_rescale(ha, rest, 0) == 0, H.ref_last_error()
+    res3 = np.empty((batch, towers - 1, n), np.uint64)
+    H.ref_polys_store(ha, p(res3))
+    assert np.array_equal(res3, oracle.rescale(n, q, psi, want, 0, 0))
+    H.ref_polys_free(ha); H.ref_polys_free(hb)
+    H.ref_ctx_destroy(rest); H.ref_ctx_destroy(ctx)
