@@ -9,7 +9,7 @@
  * is oracle/hook_patch.py (applied to a temporary copy of the reference headers).
  *
  * The templates are duck-typed on OpenFHE's PolyImpl<NativeVector> (GetValues, GetModulus,
- * GetRootOfUnity, GetRingDimension, SetValues) so this header needs no OpenFHE include.  Two forms:
+ * GetRootOfUnity, GetRingDimension, SetValues, OverrideFormat) so this header needs no OpenFHE include.  Two forms:
  * copy-per-call (dcrt_eq / dcrt_switch_format: operands live in host memory between calls, like the fork's; needs
  * no change to the class layout) and resident (Resident / resident_eq / resident_switch_format below: the towers
  * stay in HBM between hooked operators).  Failures throw: there is no silent CPU fallback.
@@ -19,6 +19,7 @@
 
 #include "PimDCRTPoly.h"
 
+#include <cstring>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -128,6 +129,25 @@ struct Resident {
 inline long &resident_uploads() { static long n = 0; return n; }     /* counters for the tests */
 inline long &resident_downloads() { static long n = 0; return n; }
 
+/* one pinned staging block per process, so that a whole DCRTPoly crosses PCIe in ONE copy at pinned-memory speed
+ * (the towers themselves are separately allocated pageable vectors, dcrtpoly.h:421) */
+struct Staging {
+  std::mutex mu;
+  fhe_ctx *ctx = nullptr;
+  void *p = nullptr;
+  size_t bytes = 0;
+  uint64_t *need(fhe_ctx *c, size_t n) {          /* call with mu held */
+    if (n > bytes || c != ctx) {
+      if (p) fhe_host_free(ctx, p);
+      p = nullptr; bytes = 0; ctx = c;
+      PimManager::check(fhe_host_alloc(c, n, &p), "pim hook: pinned staging");
+      bytes = n;
+    }
+    return static_cast<uint64_t *>(p);
+  }
+};
+inline Staging &staging() { static Staging s; return s; }
+
 /* makes `towers` resident (uploading them if they are not yet) and returns the device copy */
 template <class Towers>
 inline std::shared_ptr<Resident> ensure_device(PimManager *pim, const Towers &towers, std::shared_ptr<Resident> &res) {
@@ -139,9 +159,14 @@ inline std::shared_ptr<Resident> ensure_device(PimManager *pim, const Towers &to
   r->n = towers[0].GetRingDimension();
   const size_t bytes = r->n * sizeof(uint64_t);
   PimManager::check(fhe_alloc(r->ctx, r->towers * bytes, &r->d), "pim hook: device buffer");
-  for (size_t t = 0; t < r->towers; t++)
-    PimManager::check(fhe_h2d(r->ctx, r->d + t * bytes, words(towers[t].GetValues()), bytes, 0), "pim hook: upload");
-  PimManager::check(fhe_sync(r->ctx, 0), "pim hook: sync");     /* the host towers may change after this call */
+  {
+    Staging &st = staging();
+    std::lock_guard<std::mutex> lock(st.mu);
+    uint64_t *h = st.need(r->ctx, r->towers * bytes);
+    for (size_t t = 0; t < r->towers; t++) memcpy(h + t * r->n, words(towers[t].GetValues()), bytes);
+    PimManager::check(fhe_h2d(r->ctx, r->d, h, r->towers * bytes, 0), "pim hook: upload");
+    PimManager::check(fhe_sync(r->ctx, 0), "pim hook: sync");   /* the staging block is reused after this */
+  }
   resident_uploads()++;
   res = r;
   return r;
@@ -154,11 +179,16 @@ inline void sync_host(Towers &towers, const std::shared_ptr<Resident> &res, Form
   std::lock_guard<std::mutex> lock(res->mu);
   if (!res->device_newer) return;
   const size_t bytes = res->n * sizeof(uint64_t);
-  for (size_t t = 0; t < res->towers; t++) {
-    auto v = towers[t].GetValues();
-    PimManager::check(fhe_d2h(res->ctx, const_cast<uint64_t *>(words(v)), res->d + t * bytes, bytes, 0), "pim hook: download");
+  {
+    Staging &st = staging();
+    std::lock_guard<std::mutex> slock(st.mu);
+    uint64_t *h = st.need(res->ctx, res->towers * bytes);
+    PimManager::check(fhe_d2h(res->ctx, h, res->d, res->towers * bytes, 0), "pim hook: download");
     PimManager::check(fhe_sync(res->ctx, 0), "pim hook: sync");
-    towers[t].SetValues(std::move(v), format);
+    for (size_t t = 0; t < res->towers; t++) {       /* in place: same length and modulus */
+      memcpy(const_cast<uint64_t *>(words(towers[t].GetValues())), h + t * res->n, bytes);
+      towers[t].OverrideFormat(format);               /* poly.h:179-181: sets the format without transforming */
+    }
   }
   resident_downloads()++;
   res->device_newer = false;
