@@ -207,6 +207,26 @@ inline bool resident_eq(PimManager *pim, const Towers &a, std::shared_ptr<Reside
   return true;
 }
 
+/* out = a (op) b, out-of-place (Plus / Minus / Times, dcrtpoly.h:164-200, dcrtpoly-impl.h:398-407): `out` holds
+ * allocated host towers of the right shape; only its device copy is written and marked newer. */
+template <class Towers>
+inline bool resident_binary(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &b,
+                            std::shared_ptr<Resident> &rb, const Towers &out, std::shared_ptr<Resident> &rout, int op) {
+  if (!pim || a.empty() || a.size() != b.size() || out.size() != a.size()) return false;
+  auto da = ensure_device(pim, a, ra);
+  auto db = (&a == &b) ? da : ensure_device(pim, b, rb);
+  auto r = std::make_shared<Resident>();
+  r->ring = da->ring;
+  r->ctx = da->ctx;
+  r->towers = da->towers;
+  r->n = da->n;
+  PimManager::check(fhe_alloc(r->ctx, r->towers * r->n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
+  PimManager::check(fhe_dcrt_op(da->ring->handle(), op, r->d, da->d, db->d, 1, 0), "pim hook: dcrt op");
+  r->device_newer = true;
+  rout = r;
+  return true;
+}
+
 template <class Towers>
 inline bool resident_switch_format(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, bool to_evaluation) {
   if (!pim || a.empty()) return false;

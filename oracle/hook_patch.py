@@ -70,6 +70,16 @@ HOOK_EQ = ("\n    if (pim && pimhook::resident_eq(pim.get(), m_vectors_, pimres_
            "\n        return *this;")
 
 
+HOOK_BIN = ("        if (pim) {\n"
+            "            DCRTPolyType dev(m_params, m_format, true);\n"
+            "            if (pimhook::resident_binary(pim.get(), m_vectors_, pimres_, rhs.m_vectors_, rhs.pimres_, dev.m_vectors_,\n"
+            "                                         dev.pimres_, %s)) {\n"
+            "                dev.pim = pim;\n"
+            "                return dev;\n"
+            "            }\n"
+            "        }\n")
+
+
 def rewrite(rel, fn):
     path = os.path.join(out, rel)
     text = fn(open(path).read())
@@ -88,12 +98,21 @@ def patch_class(text):
     text = once(text, "    std::vector<PolyType> m_vectors;\n", ACCESSORS, rel)
     text = once(text, "m_vectors{e.m_vectors} {}", "m_vectors_{e.PimHostVectors()} {}", rel)
     text = once(text, "m_vectors{std::move(e.m_vectors)} {}",
-                "m_vectors_{std::move(e.m_vectors_)}, pimres_{std::move(e.pimres_)} {}", rel)
+                "m_vectors_{std::move(e.m_vectors_)}, pimres_{std::move(e.pimres_)}, pim{std::move(e.pim)} {}", rel)
     # move assignment: take the device copy along instead of forcing a download
     text = once(text, "        m_vectors = std::move(rhs.m_vectors);\n",
-                "        m_vectors_ = std::move(rhs.m_vectors_);\n        pimres_    = std::move(rhs.pimres_);\n", rel)
+                "        m_vectors_ = std::move(rhs.m_vectors_);\n        pimres_    = std::move(rhs.pimres_);\n"
+                "        pim        = std::move(rhs.pim);\n", rel)
     text = once(text, "DCRTPolyType& operator*=(const DCRTPolyType& rhs) override {",
                 "DCRTPolyType& operator*=(const DCRTPolyType& rhs) override {" + HOOK_EQ % "FHE_OP_MUL", rel)
+    # out-of-place Plus / Times: after the reference's own checks, compute on the device copies; the result carries
+    # the handle so that a chain of operators stays in HBM
+    for name, opc in (("Plus", "FHE_OP_ADD"), ("Times", "FHE_OP_MUL")):
+        start = text.index("DCRTPolyType %s(const DCRTPolyType& rhs) const override {" % name)
+        at = text.index("        DCRTPolyType tmp(m_params, m_format);\n", start)
+        # the parameter checks read only sizes and moduli: let them look at the member itself, not force a download
+        checks = text[start:at].replace("m_vectors", "m_vectors_")
+        text = text[:start] + checks + HOOK_BIN % opc + text[at:]
     # everything else in this header reads the towers through the accessor
     head, sep, tail = text.partition("namespace lbcrypto {")
     return head + "#define m_vectors PimHostVectors()\n" + sep + tail + "\n#undef m_vectors\n"
@@ -107,6 +126,11 @@ def patch_impl(text):
                 "DCRTPolyImpl<VecType>& DCRTPolyImpl<VecType>::operator+=(const DCRTPolyImpl& rhs) {" + HOOK_EQ % "FHE_OP_ADD", rel)
     text = once(text, "DCRTPolyImpl<VecType>& DCRTPolyImpl<VecType>::operator-=(const DCRTPolyImpl& rhs) {",
                 "DCRTPolyImpl<VecType>& DCRTPolyImpl<VecType>::operator-=(const DCRTPolyImpl& rhs) {" + HOOK_EQ % "FHE_OP_SUB", rel)
+    text = once(text, "    if (m_vectors.size() != rhs.m_vectors.size())\n        OPENFHE_THROW(math_error, \"tower size mismatch; cannot subtract\");\n",
+                "    if (m_vectors_.size() != rhs.m_vectors_.size())\n        OPENFHE_THROW(math_error, \"tower size mismatch; cannot subtract\");\n", rel)
+    text = once(text, "        OPENFHE_THROW(math_error, \"tower size mismatch; cannot subtract\");\n",
+                "        OPENFHE_THROW(math_error, \"tower size mismatch; cannot subtract\");\n"
+                + (HOOK_BIN % "FHE_OP_SUB").replace("DCRTPolyType dev", "DCRTPolyImpl<VecType> dev").replace("\n    ", "\n"), rel)
     text = once(text, "void DCRTPolyImpl<VecType>::SwitchFormat() {",
                 "void DCRTPolyImpl<VecType>::SwitchFormat() {"
                 "\n    if (pim) {\n"

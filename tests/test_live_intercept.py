@@ -37,6 +37,8 @@ def hooked():
     H.ref_polys_automorphism.restype = vp
     H.ref_polys_automorphism.argtypes = [vp, u32, ci]
     H.ref_polys_rescale.argtypes = [vp, vp, u64]
+    H.ref_polys_binary.restype = vp
+    H.ref_polys_binary.argtypes = [vp, vp, ci]
     return H
 
 
@@ -167,3 +169,33 @@ def test_resident_form_keeps_towers_on_the_device(hooked, oracle, pkg):
     assert np.array_equal(res3, oracle.rescale(n, q, psi, want, 0, 0))
     H.ref_polys_free(ha); H.ref_polys_free(hb)
     H.ref_ctx_destroy(rest); H.ref_ctx_destroy(ctx)
+
+
+@pytest.mark.gpu
+def test_resident_out_of_place_operators(hooked, oracle, pkg):
+    """Plus / Minus / Times of the reference's DCRTPoly (dcrtpoly.h:164-200, dcrtpoly-impl.h:398-407) with a handle
+    attached: the result is born on the device and keeps the handle, so (a + b) * b - b never touches the host until
+    it is read."""
+    H = hooked
+    n, towers, batch = 1 << 13, 3, 2
+    q, psi = oracle.gen_params(60, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    a, b = oracle.fill_ring(batch, n, q, 51), oracle.fill_ring(batch, n, q, 52)
+    ctx = H.ref_ctx_create(n, towers, p(q), p(psi))
+    ha, hb = H.ref_polys_load(ctx, p(a), batch, 0), H.ref_polys_load(ctx, p(b), batch, 0)
+    assert H.ref_polys_set_pim(ha, 1) == 0, H.ref_last_error()
+    up0, down0 = counters(H)
+    h1 = H.ref_polys_binary(ha, hb, 0)            # a + b
+    h2 = H.ref_polys_binary(h1, hb, 2)            # (a + b) * b   (the handle travelled with the result)
+    h3 = H.ref_polys_binary(h2, hb, 1)            # ... - b
+    assert counters(H) == (up0 + 2 * batch, down0)
+    res = np.empty_like(a)
+    H.ref_polys_store(h3, p(res))
+    want = octx.elementwise(1, octx.elementwise(2, octx.elementwise(0, a, b), b), b)
+    assert np.array_equal(res, want)
+    assert counters(H) == (up0 + 2 * batch, down0 + batch)
+    H.ref_polys_store(ha, p(res))                 # the operands were not modified
+    assert np.array_equal(res, a)
+    for h in (ha, hb, h1, h2, h3):
+        H.ref_polys_free(h)
+    H.ref_ctx_destroy(ctx)
