@@ -418,6 +418,41 @@ def ntt_extra(pkg, be):
             out[name] = {"ms": ms, "coeff_per_s": words / (ms * 1e-3), "hbm_gbs": 16 * words / (ms * 1e-3) / 1e9}
         be.free(src); be.free(dst)
         ring.close()
+        # RNS basis conversion (hybrid key-switching shapes): ApproxSwitchCRTBasis Q -> P, ApproxModUp, ApproxModDown, rescale
+        n, sq, sp, batch = 1 << 16, 30, 10, 16
+        q, psi = pkg.gen_params(60, n, sq + sp)
+        ring = pkg.Ring(be, n, q, psi)
+        rq, rp = pkg.RingView(ring, 0, sq), pkg.RingView(ring, sq, sp)
+        q2p, p2q, plan = pkg.Basis(rq, rp), pkg.Basis(rp, rq), pkg.Rescale(ring)
+        wq, wp = batch * sq * n, batch * sp * n
+        dq, dp, dqp, dr = be.alloc(wq * 8), be.alloc(wp * 8), be.alloc((wq + wp) * 8), be.alloc((wq + wp) * 8)
+        rq.fill_uniform(dq, batch, 20260030)
+        ring.fill_uniform(dqp, batch, 20260031)
+
+        def timed(f, reps=5):
+            for _ in range(2):
+                f()
+            be.sync()
+            be.timer_start(0)
+            for _ in range(reps):
+                f()
+            return be.timer_stop(0) / reps
+
+        ms = timed(lambda: q2p.approx_switch(dp, dq, batch))
+        out["approx_switch_crt_basis_n65536_q30_p10_b16"] = {
+            "ms": ms, "mac128_per_s": batch * n * sq * sp / (ms * 1e-3), "polys_per_s": batch / (ms * 1e-3),
+            "note": "one 64x64->128 multiply-accumulate per (source tower, target tower, coefficient)"}
+        ms = timed(lambda: q2p.approx_mod_up(dr, dq, batch, 0))
+        out["approx_mod_up_n65536_q30_p10_b16"] = {"ms": ms, "polys_per_s": batch / (ms * 1e-3)}
+        ms = timed(lambda: p2q.approx_mod_down(dq, dqp, batch, 0))
+        out["approx_mod_down_n65536_q30_p10_b16"] = {"ms": ms, "polys_per_s": batch / (ms * 1e-3)}
+        ms = timed(lambda: plan.drop_last_element_and_scale(dr, dqp, batch, 0))
+        out["drop_last_element_and_scale_n65536_t40_b16"] = {"ms": ms, "polys_per_s": batch / (ms * 1e-3)}
+        for o in (q2p, p2q, plan, rq, rp):
+            o.close()
+        for b_ in (dq, dp, dqp, dr):
+            be.free(b_)
+        ring.close()
     except Exception as ex:
         out["error"] = str(ex)[:300]
     return out

@@ -16,4 +16,9 @@ ncu --set full --clock-control none --import-source on -k regex:'ew_ring|ew_tens
     python bench.py --steps 5 --warmup 3 > $O/${R}_ncu_ew.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:ew_tensor -c 1 -o $O/${R}_prof_tensor \
     python bench.py --steps 5 --warmup 3 > $O/${R}_ncu_tensor.log 2>&1
+python tools/prof_basis.py 16 30 10 16 2 > $O/${R}_plain_basis.json 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:'basis_switch|tower_affine|rescale_spread|automorph' -c 8 \
+    -o $O/${R}_prof_basis python tools/prof_basis.py 16 30 10 16 1 > $O/${R}_ncu_basis.log 2>&1
+python tools/hook_bench.py 14 8 64 4 > $O/${R}_hook_bench.jsonl 2>&1
+python tools/hook_bench.py 16 30 8 4 >> $O/${R}_hook_bench.jsonl 2>&1
 ls -la $O | tail -20
