@@ -640,6 +640,104 @@ void orc_rescale(const orc_ctx* full, const orc_ctx* rest, const orc_ctx* last, 
     free(lastp); free(tmp); free(c); free(qlinv);
 }
 
+/* ---- BFV (HPS) set ---- */
+void orc_exact_tables(const uint64_t* q, uint32_t sq, const uint64_t* p, uint32_t sp, double* qinv, uint64_t* alpha_q_modp) {
+    for (uint32_t i = 0; i < sq; i++) qinv[i] = 1. / (double)q[i];
+    for (uint32_t j = 0; j < sp; j++) {
+        uint64_t Qm = 1 % p[j];
+        for (uint32_t k = 0; k < sq; k++) Qm = mulmod_u128(Qm, q[k] % p[j], p[j]);
+        for (uint32_t a = 0; a <= sq; a++) alpha_q_modp[(size_t)a * sp + j] = mulmod_u128(Qm, a, p[j]);
+    }
+}
+
+void orc_switch_crt_basis(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, const uint64_t* q, uint32_t sq,
+                          const uint64_t* p, uint32_t sp, const uint64_t* hat_inv, const uint64_t* hat_modp,
+                          const double* qinv, const uint64_t* alpha_q_modp) {
+    uint64_t* pre = (uint64_t*)malloc(sizeof(uint64_t) * sq);
+    u128* mu = (u128*)malloc(sizeof(u128) * sp);
+    for (uint32_t i = 0; i < sq; i++) pre[i] = orc_prep_mulconst(hat_inv[i], q[i]);
+    for (uint32_t j = 0; j < sp; j++) mu[j] = (~(u128)0) / p[j];
+    long items = (long)(B * N);
+#pragma omp parallel for schedule(static)
+    for (long e = 0; e < items; e++) {
+        size_t b = (size_t)e / N, ri = (size_t)e % N;
+        uint64_t* y = (uint64_t*)malloc(sizeof(uint64_t) * sq);
+        volatile double nu = 0.5;                                  /* :1194, :1204: separate multiply and add */
+        for (uint32_t i = 0; i < sq; i++) {
+            y[i] = orc_modmul_const(in[(b * sq + i) * N + ri], hat_inv[i], q[i], pre[i]);
+            volatile double prod = (double)y[i] * qinv[i];
+            nu = nu + prod;
+        }
+        uint32_t alpha = (uint32_t)nu;                             /* :1208 */
+        for (uint32_t j = 0; j < sp; j++) {
+            u128 cur = 0;
+            for (uint32_t i = 0; i < sq; i++) cur += (u128)y[i] * hat_modp[(size_t)i * sp + j];
+            uint64_t v = barrett128(cur, p[j], mu[j]);
+            out[(b * sp + j) * N + ri] = orc_modsub_fast(v, alpha_q_modp[(size_t)alpha * sp + j], p[j]);   /* :1226 */
+        }
+        free(y);
+    }
+    free(pre); free(mu);
+}
+
+void orc_expand_crt_basis(const orc_ctx* Q, const orc_ctx* P, uint64_t* out, const uint64_t* in, size_t B, int format,
+                          int result_format) {
+    uint32_t N = Q->N, sq = Q->T, sp = P->T;
+    size_t wq = B * sq * (size_t)N, wp = B * sp * (size_t)N;
+    uint64_t* coef = (uint64_t*)malloc(wq * 8);
+    uint64_t* partP = (uint64_t*)malloc(wp * 8);
+    uint64_t* hi = (uint64_t*)malloc(sizeof(uint64_t) * sq);
+    uint64_t* hm = (uint64_t*)malloc(sizeof(uint64_t) * sq * sp);
+    double* qinv = (double*)malloc(sizeof(double) * sq);
+    uint64_t* aq = (uint64_t*)malloc(sizeof(uint64_t) * (sq + 1) * sp);
+    memcpy(coef, in, wq * 8);
+    if (format == 0) orc_dcrt_ntt(Q, 1, coef, B, 0);                       /* :1321-1324 */
+    orc_switch_tables(Q->q, sq, P->q, sp, hi, hm);
+    orc_exact_tables(Q->q, sq, P->q, sp, qinv, aq);
+    orc_switch_crt_basis(partP, coef, B, N, Q->q, sq, P->q, sp, hi, hm, qinv, aq);
+    if (result_format == 0) orc_dcrt_ntt(P, 0, partP, B, 0);               /* :1338-1341 SetFormat(resultFormat) */
+    towers_copy(out, sq + sp, sq, partP, sp, 0, sp, B, N);
+    if (result_format == 0) {
+        if (format == 0) {
+            towers_copy(out, sq + sp, 0, in, sq, 0, sq, B, N);             /* :1346-1349 */
+        } else {
+            orc_dcrt_ntt(Q, 0, coef, B, 0);                                /* :1350-1355 */
+            towers_copy(out, sq + sp, 0, coef, sq, 0, sq, B, N);
+        }
+    } else {
+        towers_copy(out, sq + sp, 0, coef, sq, 0, sq, B, N);               /* the Q towers stay in COEFFICIENT */
+    }
+    free(coef); free(partP); free(hi); free(hm); free(qinv); free(aq);
+}
+
+void orc_scale_and_round(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, uint32_t sI, const uint64_t* o, uint32_t sO,
+                         int out_last, const double* frac, const uint64_t* modo) {
+    uint32_t T = sI + sO, in0 = out_last ? 0 : sO, out0 = out_last ? sI : 0;
+    u128* mu = (u128*)malloc(sizeof(u128) * sO);
+    for (uint32_t j = 0; j < sO; j++) mu[j] = (~(u128)0) / o[j];
+    long items = (long)(B * N);
+#pragma omp parallel for schedule(static)
+    for (long e = 0; e < items; e++) {
+        size_t b = (size_t)e / N, ri = (size_t)e % N;
+        volatile double nu = 0.5;                                              /* :1908-1913 */
+        for (uint32_t i = 0; i < sI; i++) {
+            volatile double prod = frac[i] * (double)in[(b * T + in0 + i) * N + ri];
+            nu = nu + prod;
+        }
+        int small = nu <= 18446744073709551616.0;                              /* isConvertableToNativeInt, utilities.h:133-137 */
+        u128 alpha = small ? (u128)(uint64_t)nu : (u128)nu;
+        for (uint32_t j = 0; j < sO; j++) {
+            u128 cur = 0;
+            for (uint32_t i = 0; i < sI; i++) cur += (u128)in[(b * T + in0 + i) * N + ri] * modo[(size_t)j * (sI + 1) + i];
+            cur += (u128)in[(b * T + out0 + j) * N + ri] * modo[(size_t)j * (sI + 1) + sI];
+            uint64_t v = barrett128(cur, o[j], mu[j]);
+            uint64_t a = small ? (uint64_t)(alpha % o[j]) : barrett128(alpha, o[j], mu[j]);   /* :1929-1931 / :1952 */
+            out[(b * sO + j) * N + ri] = orc_modadd_fast(v, a, o[j]);
+        }
+    }
+    free(mu);
+}
+
 int orc_max_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

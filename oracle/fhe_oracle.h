@@ -113,6 +113,24 @@ void orc_approx_mod_down(const orc_ctx* Q, const orc_ctx* P, uint64_t* out, cons
 void orc_rescale(const orc_ctx* full, const orc_ctx* rest, const orc_ctx* last, uint64_t* out, const uint64_t* in,
                  size_t B, int format, uint64_t t);
 
+/* ---- BFV (HPS) set: exact basis switch and scaling (second half) ----
+ * DCRTPolyImpl::SwitchCRTBasis (dcrtpoly-impl.h:1178-1230): like ApproxSwitchCRTBasis, plus the number of q-overflows
+ * alpha = (unsigned)(0.5 + sum_i double(y_i) * qinv[i]) (IEEE double, products and sums in index order, no fused
+ * multiply-add) and out_j = sum_j mod p_j - [alpha*Q]_{p_j}.  qinv[i] = 1./double(q_i) and alpha_q_modp[a*sp+j] as
+ * bfvrns-cryptoparameters.cpp:270-273, 343-350. */
+void orc_exact_tables(const uint64_t* q, uint32_t sq, const uint64_t* p, uint32_t sp, double* qinv, uint64_t* alpha_q_modp);
+void orc_switch_crt_basis(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, const uint64_t* q, uint32_t sq,
+                          const uint64_t* p, uint32_t sp, const uint64_t* hat_inv, const uint64_t* hat_modp,
+                          const double* qinv, const uint64_t* alpha_q_modp);
+/* DCRTPolyImpl::ExpandCRTBasis (dcrtpoly-impl.h:1311-1358): in over Q (format 0/1) -> out over QP in result_format */
+void orc_expand_crt_basis(const orc_ctx* Q, const orc_ctx* P, uint64_t* out, const uint64_t* in, size_t B, int format,
+                          int result_format);
+/* DCRTPolyImpl::ScaleAndRound(paramsOutput, ...) (dcrtpoly-impl.h:1876-1960, HAVE_INT128 branch): in over
+ * [B][sI+sO][N]; the output moduli o[sO] are the LAST sO towers when out_last != 0 (input index 0), else the first
+ * (input index sO).  frac[sI], modo[sO][sI+1] row-major as the scheme precomputes them. */
+void orc_scale_and_round(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, uint32_t sI, const uint64_t* o, uint32_t sO,
+                         int out_last, const double* frac, const uint64_t* modo);
+
 /* ---- seeded input generator shared with the product's device-side fill
  * (counter based: value i depends only on (seed, i, q)) ---- */
 uint64_t orc_uniform_at(uint64_t seed, uint64_t i, uint64_t q);

@@ -393,6 +393,113 @@ int ref_polys_rescale(ref_polys* a, ref_ctx* rest, uint64_t t) {
     return rc;
 }
 
+// ---- BFV (HPS) set: SwitchCRTBasis / ExpandCRTBasis / ScaleAndRound ---------------------------------------
+// Tables as src/pke/lib/scheme/bfvrns/bfvrns-cryptoparameters.cpp builds them for multTech == HPS:
+//   qInv[i] = 1. / double(q_i)                                   :270-273
+//   alphaQModp[a][j] = [a * Q]_{p_j}, a = 0..sizeQ               :343-350
+//   QHatModp[j][i] = [Q/q_i]_{p_j} (note the [j][i] order)       (m_QlHatModr)
+struct ref_exact_tables {
+    ref_switch_tables sw;
+    std::vector<std::vector<NativeInteger>> hatModpT, alphaQModp;
+    std::vector<double> qInv;
+};
+static ref_exact_tables make_exact_tables(const std::vector<NativeInteger>& mq, const std::vector<NativeInteger>& mp) {
+    ref_exact_tables t;
+    t.sw = make_switch_tables(mq, mp);
+    size_t sq = mq.size(), sp = mp.size();
+    t.hatModpT.assign(sp, std::vector<NativeInteger>(sq));
+    for (size_t i = 0; i < sq; i++)
+        for (size_t j = 0; j < sp; j++) t.hatModpT[j][i] = t.sw.hatModp[i][j];
+    BigInteger Q(1);
+    for (auto& q : mq) Q *= BigInteger(q);
+    t.alphaQModp.resize(sq + 1);
+    for (size_t j = 0; j < sp; j++) {
+        NativeInteger QModpj = Q.Mod(BigInteger(mp[j])).ConvertToInt();
+        for (size_t a = 0; a < sq + 1; a++) t.alphaQModp[a].push_back(QModpj.ModMul(NativeInteger(a), mp[j]));
+    }
+    t.qInv.resize(sq);
+    for (size_t i = 0; i < sq; i++) t.qInv[i] = 1. / static_cast<double>(mq[i].ConvertToInt());
+    return t;
+}
+
+// DCRTPoly::SwitchCRTBasis (dcrtpoly-impl.h:1178-1230): batch over Q -> new batch over P
+ref_polys* ref_polys_switch_crt_basis(const ref_polys* a, ref_ctx* to) {
+    auto t  = make_exact_tables(moduli_of(a->ctx), moduli_of(to));
+    auto* r = new ref_polys{to, {}};
+    serial_omp([&] {
+        for (auto& poly : a->v)
+            r->v.push_back(poly.SwitchCRTBasis(to->params, t.sw.hatInv, t.sw.hatInvPrecon, t.hatModpT, t.alphaQModp, t.sw.mu, t.qInv));
+    });
+    return r;
+}
+
+// DCRTPoly::ExpandCRTBasis (dcrtpoly-impl.h:1311-1358), in place: Q -> QP; result_format 0 EVALUATION, 1 COEFFICIENT
+int ref_polys_expand_crt_basis(ref_polys* a, ref_ctx* P, ref_ctx* QP, int result_format) {
+    int rc = 0;
+    std::string err;
+    serial_omp([&] {
+        try {
+            auto t = make_exact_tables(moduli_of(a->ctx), moduli_of(P));
+            for (auto& poly : a->v)
+                poly.ExpandCRTBasis(QP->params, P->params, t.sw.hatInv, t.sw.hatInvPrecon, t.hatModpT, t.alphaQModp, t.sw.mu, t.qInv,
+                                    result_format == 0 ? Format::EVALUATION : Format::COEFFICIENT);
+            a->ctx = QP;
+        }
+        catch (const std::exception& e) { err = e.what(); rc = 1; }
+    });
+    if (rc) g_ref_err = err;
+    return rc;
+}
+
+// ScaleAndRound tables for the HPS multiplication, t * R / (Q*R) from QR down to R (bfvrns-cryptoparameters.cpp:278-311):
+// frac [sizeQ], modr [sizeR][sizeQ+1] (row-major)
+static void make_scale_tables(const std::vector<NativeInteger>& mq, const std::vector<NativeInteger>& mr, uint64_t tval,
+                              std::vector<double>& frac, std::vector<std::vector<NativeInteger>>& modr) {
+    BigInteger R(1), QR(1), t(tval);
+    for (auto& r : mr) R *= BigInteger(r);
+    for (auto& q : mq) QR *= BigInteger(q);
+    QR *= R;
+    frac.resize(mq.size());
+    for (size_t i = 0; i < mq.size(); i++) {
+        BigInteger qi(mq[i].ConvertToInt());
+        frac[i] = static_cast<double>(((QR.DividedBy(qi)).ModInverse(qi) * R * t).Mod(qi).ConvertToInt()) /
+                  static_cast<double>(qi.ConvertToInt());
+    }
+    modr.assign(mr.size(), {});
+    for (size_t j = 0; j < mr.size(); j++) {
+        BigInteger rj(mr[j].ConvertToInt());
+        for (size_t i = 0; i < mq.size(); i++) {
+            BigInteger qi(mq[i].ConvertToInt());
+            BigInteger v = (t * R * ((QR.DividedBy(qi)).ModInverse(qi))) / qi;
+            modr[j].push_back(v.Mod(rj).ConvertToInt());
+        }
+        BigInteger v = (t * R * ((QR.DividedBy(rj)).ModInverse(rj))) / rj;
+        modr[j].push_back(v.Mod(rj).ConvertToInt());
+    }
+}
+void ref_scale_tables_get(const ref_ctx* Q, const ref_ctx* R, uint64_t t, double* frac, uint64_t* modr) {
+    std::vector<double> f;
+    std::vector<std::vector<NativeInteger>> m;
+    make_scale_tables(moduli_of(Q), moduli_of(R), t, f, m);
+    for (size_t i = 0; i < f.size(); i++) frac[i] = f[i];
+    for (size_t j = 0; j < m.size(); j++)
+        for (size_t i = 0; i < m[j].size(); i++) modr[j * m[j].size() + i] = m[j][i].ConvertToInt();
+}
+
+// DCRTPoly::ScaleAndRound(paramsOutput, ...) (dcrtpoly-impl.h:1876-1960): batch over QR -> new batch over R
+ref_polys* ref_polys_scale_and_round(const ref_polys* a, ref_ctx* Q, ref_ctx* R, uint64_t t) {
+    std::vector<double> frac;
+    std::vector<std::vector<NativeInteger>> modr;
+    auto mr = moduli_of(R);
+    make_scale_tables(moduli_of(Q), mr, t, frac, modr);
+    auto mu = make_switch_tables(moduli_of(Q), mr).mu;
+    auto* r = new ref_polys{R, {}};
+    serial_omp([&] {
+        for (auto& poly : a->v) r->v.push_back(poly.ScaleAndRound(R->params, modr, frac, mu));
+    });
+    return r;
+}
+
 // mod-ops of the PimData surface executed by the reference's own NativeVector (in-place forms:
 // mubintvecnat.cpp:111-195,370-487, mubintvecnat.h:560-566).  kind = enum mod_kernel.
 // Returns 0, or 1 if the reference threw.

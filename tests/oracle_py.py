@@ -50,6 +50,10 @@ class Oracle:
             ("orc_approx_mod_up", None, [vp, vp, vp, vp, sz, ci]),
             ("orc_approx_mod_down", None, [vp, vp, vp, vp, sz, u64]),
             ("orc_rescale", None, [vp, vp, vp, vp, vp, sz, ci, u64]),
+            ("orc_exact_tables", None, [vp, u32, vp, u32, vp, vp]),
+            ("orc_switch_crt_basis", None, [vp, vp, sz, u32, vp, u32, vp, u32, vp, vp, vp, vp]),
+            ("orc_expand_crt_basis", None, [vp, vp, vp, vp, sz, ci, ci]),
+            ("orc_scale_and_round", None, [vp, vp, sz, u32, u32, vp, u32, ci, vp, vp]),
             ("orc_uniform_at", u64, [u64, u64, u64]), ("orc_fill_uniform", None, [vp, sz, u64, u64, u64]),
         ]:
             f = getattr(L, name)
@@ -202,6 +206,48 @@ class OracleBasis:
         out = np.empty((B, self.sq, self.n), np.uint64)
         self.o.L.orc_approx_mod_down(self.Q.h, self.P.h, _p(out), _p(x), B, t)
         return out
+
+
+def _exact_tables(self):
+    qinv, aq = np.empty(self.sq, np.float64), np.empty((self.sq + 1, self.sp), np.uint64)
+    self.o.L.orc_exact_tables(_p(self.Q.q), self.sq, _p(self.P.q), self.sp, _p(qinv), _p(aq))
+    return qinv, aq
+
+
+def _switch_exact(self, x):
+    hi, hm = self.tables(False)
+    qinv, aq = self.exact_tables()
+    x = np.ascontiguousarray(x, np.uint64)
+    B = x.size // (self.sq * self.n)
+    out = np.empty((B, self.sp, self.n), np.uint64)
+    self.o.L.orc_switch_crt_basis(_p(out), _p(x), B, self.n, _p(self.Q.q), self.sq, _p(self.P.q), self.sp, _p(hi), _p(hm),
+                                  _p(qinv), _p(aq))
+    return out
+
+
+def _expand(self, x, fmt, result_fmt):
+    x = np.ascontiguousarray(x, np.uint64)
+    B = x.size // (self.sq * self.n)
+    out = np.empty((B, self.sq + self.sp, self.n), np.uint64)
+    self.o.L.orc_expand_crt_basis(self.Q.h, self.P.h, _p(out), _p(x), B, fmt, result_fmt)
+    return out
+
+
+def _scale_and_round(self, x, frac, modo, out_last=1):
+    """ScaleAndRound of [B][Q+P][N] down to the P towers (out_last) or the Q towers."""
+    x = np.ascontiguousarray(x, np.uint64)
+    B = x.size // ((self.sq + self.sp) * self.n)
+    o, sI = (self.P.q, self.sq) if out_last else (self.Q.q, self.sp)
+    out = np.empty((B, len(o), self.n), np.uint64)
+    frac, modo = np.ascontiguousarray(frac, np.float64), np.ascontiguousarray(modo, np.uint64)
+    self.o.L.orc_scale_and_round(_p(out), _p(x), B, self.n, sI, _p(o), len(o), out_last, _p(frac), _p(modo))
+    return out
+
+
+OracleBasis.exact_tables = _exact_tables
+OracleBasis.switch_exact = _switch_exact
+OracleBasis.expand = _expand
+OracleBasis.scale_and_round = _scale_and_round
 
 
 def _rescale(self, n, q, psi, x, fmt, t=0):

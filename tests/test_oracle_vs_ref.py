@@ -42,6 +42,12 @@ def ref():
     R.ref_polys_rescale.argtypes = [vp, vp, u64]
     R.ref_switch_tables_get.argtypes = [vp, vp, vp, vp]
     R.ref_rescale_tables_get.argtypes = [vp, vp, vp]
+    R.ref_polys_switch_crt_basis.restype = vp
+    R.ref_polys_switch_crt_basis.argtypes = [vp, vp]
+    R.ref_polys_expand_crt_basis.argtypes = [vp, vp, vp, ci]
+    R.ref_scale_tables_get.argtypes = [vp, vp, u64, vp, vp]
+    R.ref_polys_scale_and_round.restype = vp
+    R.ref_polys_scale_and_round.argtypes = [vp, vp, vp, u64]
     return R
 
 
@@ -177,4 +183,45 @@ def test_basis_conversion_matches_reference(oracle, ref, nbits, n, sq, sp):
             assert np.array_equal(res, oracle.rescale(n, q, psi, y, fmt, t)), f"rescale t={t} format {fmt}"
             ref.ref_polys_free(hy)
     for c in (cQ, cP, cQP, cR):
+        ref.ref_ctx_destroy(c)
+
+
+@pytest.mark.parametrize("nbits,n,sq,sp,t", [(30, 16, 2, 3, 65537), (60, 64, 3, 4, 65537), (60, 1 << 10, 5, 6, 786433),
+                                               (55, 1 << 11, 20, 21, 65537), (60, 16, 80, 81, 65537)])
+def test_bfv_hps_set_matches_reference(oracle, ref, nbits, n, sq, sp, t):
+    """SURVEY §8(f) rank 3, BFV half: SwitchCRTBasis, ExpandCRTBasis and ScaleAndRound of the reference's DCRTPoly
+    (IEEE-double overflow count included) vs the restatement; tables as bfvrns-cryptoparameters.cpp builds them."""
+    q, psi = oracle.gen_params(nbits, n, sq + sp)
+    ob = oracle.basis(n, q, psi, sq)
+    mk = lambda a, b: ref.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+    cQ, cP, cQP = mk(0, sq), mk(sq, sq + sp), mk(0, sq + sp)
+    B = 2
+    x = oracle.fill_ring(B, n, q[:sq].copy(), 61)
+    x[0, :, 0] = q[:sq] - 1
+    x[0, :, 1] = 0
+    hx = ref.ref_polys_load(cQ, p(x), B, 1)
+    hr = ref.ref_polys_switch_crt_basis(hx, cP)
+    res = np.empty((B, sp, n), np.uint64)
+    ref.ref_polys_store(hr, p(res))
+    assert np.array_equal(res, ob.switch_exact(x))
+    ref.ref_polys_free(hr); ref.ref_polys_free(hx)
+    for fmt in (0, 1):
+        for rf in (0, 1):
+            hx = ref.ref_polys_load(cQ, p(x), B, fmt)
+            assert ref.ref_polys_expand_crt_basis(hx, cP, cQP, rf) == 0, ref.ref_last_error()
+            res = np.empty((B, sq + sp, n), np.uint64)
+            ref.ref_polys_store(hx, p(res))
+            assert np.array_equal(res, ob.expand(x, fmt, rf)), f"ExpandCRTBasis {fmt}->{rf}"
+            ref.ref_polys_free(hx)
+    frac, modr = np.empty(sq, np.float64), np.empty((sp, sq + 1), np.uint64)
+    ref.ref_scale_tables_get(cQ, cP, t, p(frac), p(modr))
+    y = oracle.fill_ring(B, n, q, 62)
+    y[0, :, 0] = q - 1
+    hy = ref.ref_polys_load(cQP, p(y), B, 1)
+    hr = ref.ref_polys_scale_and_round(hy, cQ, cP, t)
+    res = np.empty((B, sp, n), np.uint64)
+    ref.ref_polys_store(hr, p(res))
+    assert np.array_equal(res, ob.scale_and_round(y, frac, modr, 1))
+    ref.ref_polys_free(hr); ref.ref_polys_free(hy)
+    for c in (cQ, cP, cQP):
         ref.ref_ctx_destroy(c)
