@@ -30,6 +30,8 @@
  *     dcrtpoly-impl.h:348-369, poly-impl.h:312-380
  *   DCRTPolyImpl::ApproxSwitchCRTBasis / ApproxModUp /          fhe_approx_switch_crt_basis / fhe_approx_mod_up /
  *     ApproxModDown   dcrtpoly-impl.h:1034-1175                   fhe_approx_mod_down
+ *   DCRTPolyImpl::SwitchCRTBasis / ExpandCRTBasis /              fhe_switch_crt_basis / fhe_expand_crt_basis /
+ *     ScaleAndRound   dcrtpoly-impl.h:1178-1358, 1876-1960        fhe_scale_and_round
  *   DCRTPolyImpl::DropLastElementAndScale / ModReduce            fhe_drop_last_element_and_scale / fhe_mod_reduce
  *     dcrtpoly-impl.h:746-812
  *   FirstPrime / PreviousPrime / RootOfUnity parameter recipe    fhe_gen_params (host side, setup only)
@@ -187,6 +189,26 @@ int fhe_approx_mod_up(fhe_basis* q_to_p, fhe_dptr dst_qp, fhe_dptr src_q, size_t
  * [t^-1]_{p_j} and the switched part by t, bgvrns-cryptoparameters.cpp:83-88).  [P^-1]_{q_i}
  * (rns-cryptoparameters.cpp:190-197) is derived from the moduli. */
 int fhe_approx_mod_down(fhe_basis* p_to_q, fhe_dptr dst_q, fhe_dptr src_qp, size_t batch, uint64_t t, int stream);
+
+/* DCRTPolyImpl::SwitchCRTBasis (dcrtpoly-impl.h:1178-1230): the exact form — counts the q-overflows in IEEE double
+ * (`nu = 0.5 + sum_i double(y_i) * (1./double(q_i))`, in index order, not fused) and subtracts [alpha*Q]_{p_j}; the
+ * tables of bfvrns-cryptoparameters.cpp:270-273, 343-350 are derived from the moduli. */
+int fhe_switch_crt_basis(fhe_basis* basis, fhe_dptr dst, fhe_dptr src, size_t batch, int stream);
+/* DCRTPolyImpl::ExpandCRTBasis (dcrtpoly-impl.h:1311-1358) with basis = Q -> P: src over Q in `format` -> dst over QP
+ * [batch][sq+sp][N] in `result_format` (0 EVALUATION, 1 COEFFICIENT).  src is not modified. */
+int fhe_expand_crt_basis(fhe_basis* q_to_p, fhe_dptr dst_qp, fhe_dptr src_q, size_t batch, int format, int result_format,
+                         int stream);
+
+typedef struct fhe_scale_round fhe_scale_round;
+/* DCRTPolyImpl::ScaleAndRound(paramsOutput, tOSHatInvModsDivsModo, tOSHatInvModsDivsFrac, modoBarretMu)
+ * (dcrtpoly-impl.h:1876-1960): `ring` = the input basis (sI + size_out towers); the output moduli are its last
+ * size_out towers when out_last != 0 (the reference's "output modulus is P" case), else its first.  frac [sI] and
+ * modo [size_out][sI+1] (row-major) are the scheme's tables (bfvrns-cryptoparameters.cpp:278-311); the 128-bit
+ * Barrett constants are built here.  Format is whatever src is in (the schemes call it in COEFFICIENT). */
+int fhe_scale_round_create(fhe_ring* ring, uint32_t size_out, int out_last, const double* frac, const uint64_t* modo,
+                           fhe_scale_round** out);
+int fhe_scale_round_destroy(fhe_scale_round* plan);
+int fhe_scale_and_round(fhe_scale_round* plan, fhe_dptr dst, fhe_dptr src, size_t batch, int stream);
 
 typedef struct fhe_rescale fhe_rescale;  /* constants for dropping the last tower of `ring` */
 /* qlql [T-1] = [Ql*[Ql^-1]_{ql}/ql]_{q_i} and qlinv [T-1] = [ql^-1]_{q_i}

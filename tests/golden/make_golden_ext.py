@@ -91,6 +91,64 @@ def basis_section(R, O, p):
     return out
 
 
+BFV_CASES = [  # nbits, N, sizeQ, sizeP (= R), batch, seed, t
+    (30, 16, 2, 3, 2, 20263001, 65537),
+    (60, 1 << 10, 4, 5, 2, 20263002, 65537),
+    (60, 1 << 13, 6, 7, 1, 20263003, 786433),
+    (60, 16, 80, 81, 1, 20263004, 65537),          # nu >= 2^64: the 128-bit alpha path of ScaleAndRound
+]
+
+
+def bfv_section(R, O, p):
+    """Section "bfv": SwitchCRTBasis, ExpandCRTBasis (all format pairs) and ScaleAndRound (QR -> R) run by the reference
+    (dcrtpoly-impl.h:1178-1358, 1876-1960) with tables built as bfvrns-cryptoparameters.cpp:262-350 does; the
+    ScaleAndRound tables are stored so that the GPU box can feed the same ones."""
+    R.ref_polys_switch_crt_basis.restype = vp
+    R.ref_polys_switch_crt_basis.argtypes = [vp, vp]
+    R.ref_polys_expand_crt_basis.argtypes = [vp, vp, vp, ci]
+    R.ref_scale_tables_get.argtypes = [vp, vp, u64, vp, vp]
+    R.ref_polys_scale_and_round.restype = vp
+    R.ref_polys_scale_and_round.argtypes = [vp, vp, vp, u64]
+    out = []
+    for nbits, n, sq, sp, batch, seed, t in BFV_CASES:
+        q, psi = np.zeros(sq + sp, np.uint64), np.zeros(sq + sp, np.uint64)
+        R.ref_gen_params(nbits, n, sq + sp, p(q), p(psi))
+        mk = lambda a, b: R.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+        cQ, cP, cQP = mk(0, sq), mk(sq, sq + sp), mk(0, sq + sp)
+        x = O.fill_ring(batch, n, q[:sq].copy(), seed)
+        y = O.fill_ring(batch, n, q, seed + 1)
+        frac, modr = np.empty(sq, np.float64), np.empty((sp, sq + 1), np.uint64)
+        R.ref_scale_tables_get(cQ, cP, t, p(frac), p(modr))
+        rec = {"nbits": nbits, "N": n, "sizeQ": sq, "sizeP": sp, "batch": batch, "seed": seed, "t": t,
+               "q": [int(v) for v in q], "psi": [int(v) for v in psi], "sha_x": digest(x), "sha_y": digest(y),
+               "frac_hex": [float(v).hex() for v in frac], "modr": [int(v) for v in modr.reshape(-1)]}
+        hx = R.ref_polys_load(cQ, p(x), batch, 1)
+        hr = R.ref_polys_switch_crt_basis(hx, cP)
+        res = np.empty((batch, sp, n), np.uint64)
+        R.ref_polys_store(hr, p(res))
+        rec["sha_switch_exact"] = digest(res)
+        R.ref_polys_free(hr); R.ref_polys_free(hx)
+        for fmt in (0, 1):
+            for rf in (0, 1):
+                hx = R.ref_polys_load(cQ, p(x), batch, fmt)
+                assert R.ref_polys_expand_crt_basis(hx, cP, cQP, rf) == 0
+                res = np.empty((batch, sq + sp, n), np.uint64)
+                R.ref_polys_store(hx, p(res))
+                rec[f"sha_expand_f{fmt}_r{rf}"] = digest(res)
+                R.ref_polys_free(hx)
+        hy = R.ref_polys_load(cQP, p(y), batch, 1)
+        hr = R.ref_polys_scale_and_round(hy, cQ, cP, t)
+        res = np.empty((batch, sp, n), np.uint64)
+        R.ref_polys_store(hr, p(res))
+        rec["sha_scale_round"] = digest(res)
+        R.ref_polys_free(hr); R.ref_polys_free(hy)
+        for c in (cQ, cP, cQP):
+            R.ref_ctx_destroy(c)
+        out.append(rec)
+        print("bfv case", n, sq, sp, "done")
+    return out
+
+
 def main():
     R = ctypes.CDLL(oracle_py.REF_SO)
     R.ref_gen_params.argtypes = [u32, u32, u32, vp, vp]
@@ -133,6 +191,7 @@ def main():
         auto.append(rec)
         print("automorphism case", n, towers, "done")
     basis = basis_section(R, O, p)
+    bfv = bfv_section(R, O, p)
     path = os.path.join(ROOT, "tests", "golden", "ext_vectors.json")
     doc = {}
     if os.path.exists(path):
@@ -142,6 +201,7 @@ def main():
                         "(reference commit e70da11 compiled by oracle/Makefile)")
     doc["automorphism"] = auto
     doc["basis"] = basis
+    doc["bfv"] = bfv
     with open(path, "w") as f:
         json.dump(doc, f, indent=1)
     print("wrote", path)

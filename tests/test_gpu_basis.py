@@ -189,3 +189,81 @@ def test_basis_conversion_reference_golden(pkg, backend, oracle, case):
         o.close()
     d.close()
     ring.close()
+
+
+# ---- BFV (HPS) half of rank 3: SwitchCRTBasis, ExpandCRTBasis, ScaleAndRound ---------------------------------
+@pytest.mark.parametrize("nbits,n,sq,sp,batch", [(30, 16, 2, 3, 2), (60, 64, 3, 4, 3), (60, 1 << 10, 5, 6, 2),
+                                                 (55, 1 << 12, 9, 12, 1), (60, 1 << 14, 4, 5, 2)])
+def test_exact_switch_and_expand_vs_oracle(pkg, backend, oracle, nbits, n, sq, sp, batch):
+    q, psi, ring, rq, rp, ob = setup(pkg, backend, oracle, nbits, n, sq, sp)
+    d = Dev(backend)
+    q2p = pkg.Basis(rq, rp)
+    x = oracle.fill_ring(batch, n, q[:sq].copy(), 71)
+    x[0, :, 0] = q[:sq] - 1
+    x[0, :, 1] = 0
+    dx, dp, dqp = d.put(x), d.new(batch * sp * n), d.new(batch * (sq + sp) * n)
+    q2p.switch_crt_basis(dp, dx, batch)
+    assert np.array_equal(backend.d2h(dp, batch * sp * n).reshape(batch, sp, n), ob.switch_exact(x))
+    for fmt in (0, 1):
+        for rf in (0, 1):
+            q2p.expand_crt_basis(dqp, dx, batch, fmt, rf)
+            got = backend.d2h(dqp, batch * (sq + sp) * n).reshape(batch, sq + sp, n)
+            assert np.array_equal(got, ob.expand(x, fmt, rf)), f"ExpandCRTBasis {fmt}->{rf}"
+    assert np.array_equal(backend.d2h(dx, x.size).reshape(x.shape), x), "source modified"
+    q2p.approx_switch(dp, dx, batch)                       # the approximate form still works on the same basis object
+    assert np.array_equal(backend.d2h(dp, batch * sp * n).reshape(batch, sp, n), ob.approx_switch(x))
+    for o in (q2p, rq, rp):
+        o.close()
+    d.close()
+    ring.close()
+
+
+@pytest.mark.parametrize("case", EXT["bfv"], ids=lambda c: f"N{c['N']}_Q{c['sizeQ']}_P{c['sizeP']}")
+def test_bfv_set_reference_golden(pkg, backend, oracle, case):
+    """Against the reference's digests, with the reference's own ScaleAndRound tables (stored in the fixture)."""
+    n, sq, sp, batch = case["N"], case["sizeQ"], case["sizeP"], case["batch"]
+    q, psi = np.array(case["q"], np.uint64), np.array(case["psi"], np.uint64)
+    ring = pkg.Ring(backend, n, q, psi)
+    rq, rp = pkg.RingView(ring, 0, sq), pkg.RingView(ring, sq, sp)
+    q2p = pkg.Basis(rq, rp)
+    frac = np.array([float.fromhex(v) for v in case["frac_hex"]], np.float64)
+    modr = np.array(case["modr"], np.uint64).reshape(sp, sq + 1)
+    plan = pkg.ScaleRound(ring, sp, frac, modr, out_last=True)
+    x = oracle.fill_ring(batch, n, q[:sq].copy(), case["seed"])
+    y = oracle.fill_ring(batch, n, q, case["seed"] + 1)
+    assert digest(x) == case["sha_x"] and digest(y) == case["sha_y"]
+    d = Dev(backend)
+    dx, dy, out = d.put(x), d.put(y), d.new(batch * (sq + sp) * n)
+    q2p.switch_crt_basis(out, dx, batch)
+    assert digest(backend.d2h(out, batch * sp * n)) == case["sha_switch_exact"]
+    for fmt in (0, 1):
+        for rf in (0, 1):
+            q2p.expand_crt_basis(out, dx, batch, fmt, rf)
+            assert digest(backend.d2h(out, batch * (sq + sp) * n)) == case[f"sha_expand_f{fmt}_r{rf}"], (fmt, rf)
+    plan.scale_and_round(out, dy, batch)
+    got = backend.d2h(out, batch * sp * n)
+    assert digest(got) == case["sha_scale_round"]
+    assert np.array_equal(got.reshape(batch, sp, n), oracle.basis(n, q, psi, sq).scale_and_round(y, frac, modr, 1))
+    for o in (plan, q2p, rq, rp):
+        o.close()
+    d.close()
+    ring.close()
+
+
+def test_scale_and_round_to_first_towers(pkg, backend, oracle):
+    """The other orientation (output = the FIRST towers, dcrtpoly-impl.h:1892-1895) with arbitrary tables."""
+    n, sq, sp, batch = 1 << 11, 3, 4, 2
+    q, psi, ring, rq, rp, ob = setup(pkg, backend, oracle, 60, n, sq, sp)
+    rng = np.random.default_rng(9)
+    frac = rng.random(sp)
+    modo = np.stack([rng.integers(0, int(m), size=sp + 1, dtype=np.uint64) for m in q[:sq]])
+    plan = pkg.ScaleRound(ring, sq, frac, modo, out_last=False)
+    y = oracle.fill_ring(batch, n, q, 81)
+    d = Dev(backend)
+    dy, out = d.put(y), d.new(batch * sq * n)
+    plan.scale_and_round(out, dy, batch)
+    assert np.array_equal(backend.d2h(out, batch * sq * n).reshape(batch, sq, n), ob.scale_and_round(y, frac, modo, 0))
+    for o in (plan, rq, rp):
+        o.close()
+    d.close()
+    ring.close()

@@ -61,6 +61,11 @@ SIGNATURES = {
     "fhe_approx_switch_crt_basis": (ci, [vp, u64, u64, sz, ci]),
     "fhe_approx_mod_up": (ci, [vp, u64, u64, sz, ci, ci]),
     "fhe_approx_mod_down": (ci, [vp, u64, u64, sz, u64, ci]),
+    "fhe_switch_crt_basis": (ci, [vp, u64, u64, sz, ci]),
+    "fhe_expand_crt_basis": (ci, [vp, u64, u64, sz, ci, ci, ci]),
+    "fhe_scale_round_create": (ci, [vp, u32, ci, vp, vp, ctypes.POINTER(vp)]),
+    "fhe_scale_round_destroy": (ci, [vp]),
+    "fhe_scale_and_round": (ci, [vp, u64, u64, sz, ci]),
     "fhe_rescale_create": (ci, [vp, vp, vp, ctypes.POINTER(vp)]),
     "fhe_rescale_destroy": (ci, [vp]),
     "fhe_rescale_tables": (ci, [vp, vp, vp]),

@@ -54,7 +54,10 @@ __device__ __forceinline__ u64 switch_modulus(u64 v, u64 half, u64 nm, u64 diff,
 
 constexpr int BS_THREADS = 256;
 
-template <int JT>
+// EXACT: DCRTPolyImpl::SwitchCRTBasis (dcrtpoly-impl.h:1178-1230): additionally counts the q-overflows
+// alpha = (unsigned)(0.5 + sum_i double(y_i) * qinv[i]) in IEEE double (round-to-nearest multiply and add, in index
+// order, never fused — what the CPU path computes) and subtracts [alpha*Q]_{p_j}.
+template <int JT, bool EXACT>
 __global__ void __launch_bounds__(BS_THREADS)
 basis_switch_kernel(u64* __restrict__ dst, const u64* __restrict__ src, size_t items, u32 logN, BasisDev bd,
                     u32 srcT, u32 src0, u32 dstT, u32 dst0) {
@@ -62,6 +65,7 @@ basis_switch_kernel(u64* __restrict__ dst, const u64* __restrict__ src, size_t i
     u64* sH = sm;                                          // [sq][JT]
     u64* sQ = sH + (size_t)bd.sq * JT;                     // [sq]
     u64* sC = sQ + bd.sq;                                  // [sq][2] {c, companion}
+    double* sI = reinterpret_cast<double*>(sC + 2 * bd.sq); // [sq] 1/q_i (EXACT only)
     const u32 j0 = blockIdx.y * JT;
     for (u32 k = threadIdx.x; k < bd.sq * JT; k += BS_THREADS) {
         u32 i = k / JT, jj = k % JT;
@@ -71,6 +75,7 @@ basis_switch_kernel(u64* __restrict__ dst, const u64* __restrict__ src, size_t i
         sQ[i] = bd.q[i];
         sC[2 * i] = bd.pre[i].x;
         sC[2 * i + 1] = bd.pre[i].y;
+        if (EXACT) sI[i] = bd.qinv[i];
     }
     __syncthreads();
     const size_t e = (size_t)blockIdx.x * BS_THREADS + threadIdx.x;
@@ -82,38 +87,124 @@ basis_switch_kernel(u64* __restrict__ dst, const u64* __restrict__ src, size_t i
     for (int jj = 0; jj < JT; jj++) { lo[jj] = 0; hi[jj] = 0; }
     const u64* sp = src + (((b * srcT) + src0) << logN) + n;
     u64 x = sp[0];
+    double nu = 0.5;
     for (u32 i = 0; i < bd.sq; i++) {
         u64 xn = (i + 1 < bd.sq) ? sp[(size_t)(i + 1) << logN] : 0ull;     // prefetch the next tower's coefficient
         u64 y = shoup(x, sC[2 * i], sC[2 * i + 1], sQ[i]);
+        if (EXACT) nu = __dadd_rn(nu, __dmul_rn(__ull2double_rn(y), sI[i]));
 #pragma unroll
         for (int jj = 0; jj < JT; jj++) mac128(lo[jj], hi[jj], y, sH[i * JT + jj]);
         x = xn;
     }
+    const u32 alpha = EXACT ? (u32)nu : 0u;
 #pragma unroll
     for (int jj = 0; jj < JT; jj++) {
         if (j0 + jj < bd.sp) {
             const BasisTarget tg = bd.tgt[j0 + jj];
             u64 r = barrett128(lo[jj], hi[jj], tg.p, tg.mu_lo, tg.mu_hi);
             if (tg.post) r = shoup(r, tg.post, tg.postp, tg.p);
+            if (EXACT) r = submod(r, bd.alphaq[(size_t)alpha * bd.sp + j0 + jj], tg.p);
             dst[(((b * dstT) + dst0 + j0 + jj) << logN) + n] = r;
         }
     }
 }
 
-cudaError_t launch_basis_switch(const BasisDev& bd, uint64_t* dst, uint32_t dstT, uint32_t dst0, const uint64_t* src,
-                                uint32_t srcT, uint32_t src0, size_t batch, uint32_t logN, cudaStream_t st) {
-    size_t items = batch << logN;
-    if (items == 0) return cudaSuccess;
+template <bool EXACT>
+static cudaError_t launch_basis_switch_t(const BasisDev& bd, u64* d, uint32_t dstT, uint32_t dst0, const u64* s, uint32_t srcT,
+                                         uint32_t src0, size_t items, uint32_t logN, cudaStream_t st) {
     int jt = bd.sp >= 8 ? 8 : bd.sp >= 4 ? 4 : bd.sp >= 2 ? 2 : 1;
     dim3 grid((unsigned)((items + BS_THREADS - 1) / BS_THREADS), (bd.sp + jt - 1) / jt);
-    size_t smem = ((size_t)bd.sq * jt + 3 * (size_t)bd.sq) * 8;
+    size_t smem = ((size_t)bd.sq * jt + 4 * (size_t)bd.sq) * 8;
+    switch (jt) {
+        case 8: basis_switch_kernel<8, EXACT><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0); break;
+        case 4: basis_switch_kernel<4, EXACT><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0); break;
+        case 2: basis_switch_kernel<2, EXACT><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0); break;
+        default: basis_switch_kernel<1, EXACT><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0); break;
+    }
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_basis_switch(const BasisDev& bd, uint64_t* dst, uint32_t dstT, uint32_t dst0, const uint64_t* src,
+                                uint32_t srcT, uint32_t src0, size_t batch, uint32_t logN, bool exact, cudaStream_t st) {
+    size_t items = batch << logN;
+    if (items == 0) return cudaSuccess;
+    u64* d = reinterpret_cast<u64*>(dst);
+    const u64* s = reinterpret_cast<const u64*>(src);
+    return exact ? launch_basis_switch_t<true>(bd, d, dstT, dst0, s, srcT, src0, items, logN, st)
+                 : launch_basis_switch_t<false>(bd, d, dstT, dst0, s, srcT, src0, items, logN, st);
+}
+
+// DCRTPolyImpl::ScaleAndRound(paramsOutput, ...) (dcrtpoly-impl.h:1876-1960, HAVE_INT128 branch).  Input [B][sI+sO][N];
+// in0 / out0 = first input / output tower.  Per coefficient: nu = 0.5 + sum_i frac[i] * double(x_i) (IEEE double, in
+// order, not fused), alpha = integer part of nu (64-bit, or 128-bit when nu >= 2^64), and for every output modulus o_j:
+// (sum_i x_i * modo[j][i] + x_out_j * modo[j][sI]) mod o_j + alpha mod o_j.
+template <int JT>
+__global__ void __launch_bounds__(BS_THREADS)
+scale_round_kernel(u64* __restrict__ dst, const u64* __restrict__ src, size_t items, u32 logN, ScaleDev sd) {
+    extern __shared__ __align__(16) u64 sm[];
+    u64* sM = sm;                                               // [sI+1][JT]
+    double* sF = reinterpret_cast<double*>(sM + (size_t)(sd.sI + 1) * JT);   // [sI]
+    const u32 j0 = blockIdx.y * JT;
+    for (u32 k = threadIdx.x; k < (sd.sI + 1) * JT; k += BS_THREADS) {
+        u32 i = k / JT, jj = k % JT;
+        sM[k] = (j0 + jj < sd.sO) ? sd.modo[(size_t)(j0 + jj) * (sd.sI + 1) + i] : 0ull;
+    }
+    for (u32 i = threadIdx.x; i < sd.sI; i += BS_THREADS) sF[i] = sd.frac[i];
+    __syncthreads();
+    const size_t e = (size_t)blockIdx.x * BS_THREADS + threadIdx.x;
+    if (e >= items) return;
+    const size_t b = e >> logN;
+    const u32 n = (u32)e & ((1u << logN) - 1);
+    const u32 T = sd.sI + sd.sO;
+    u64 lo[JT], hi[JT];
+#pragma unroll
+    for (int jj = 0; jj < JT; jj++) { lo[jj] = 0; hi[jj] = 0; }
+    const u64* ip = src + (((b * T) + sd.in0) << logN) + n;
+    double nu = 0.5;
+    u64 x = ip[0];
+    for (u32 i = 0; i < sd.sI; i++) {
+        u64 xn = (i + 1 < sd.sI) ? ip[(size_t)(i + 1) << logN] : 0ull;
+        nu = __dadd_rn(nu, __dmul_rn(sF[i], __ull2double_rn(x)));
+#pragma unroll
+        for (int jj = 0; jj < JT; jj++) mac128(lo[jj], hi[jj], x, sM[i * JT + jj]);
+        x = xn;
+    }
+    // integer part of nu: utilities.h:133-137 decides between a 64-bit and a 128-bit conversion
+    u64 a_lo, a_hi = 0;
+    if (nu < 18446744073709551616.0) {
+        a_lo = __double2ull_rz(nu);
+    } else {
+        a_hi = __double2ull_rz(nu * 5.421010862427522e-20);                  // nu / 2^64: exact (power of two)
+        a_lo = __double2ull_rz(nu - __ull2double_rn(a_hi) * 18446744073709551616.0);
+    }
+#pragma unroll
+    for (int jj = 0; jj < JT; jj++) {
+        if (j0 + jj < sd.sO) {
+            const BasisTarget tg = sd.tgt[j0 + jj];
+            u64 xo = src[(((b * T) + sd.out0 + j0 + jj) << logN) + n];
+            mac128(lo[jj], hi[jj], xo, sM[sd.sI * JT + jj]);
+            u64 r = barrett128(lo[jj], hi[jj], tg.p, tg.mu_lo, tg.mu_hi);
+            u64 a = barrett128(a_lo, a_hi, tg.p, tg.mu_lo, tg.mu_hi);
+            dst[(((b * sd.sO) + j0 + jj) << logN) + n] = addmod(r, a, tg.p);
+        }
+    }
+}
+
+cudaError_t launch_scale_round(const ScaleDev& sd, uint64_t* dst, const uint64_t* src, size_t batch, uint32_t logN,
+                               cudaStream_t st) {
+    size_t items = batch << logN;
+    if (items == 0) return cudaSuccess;
+    int jt = sd.sO >= 8 ? 8 : sd.sO >= 4 ? 4 : sd.sO >= 2 ? 2 : 1;
+    dim3 grid((unsigned)((items + BS_THREADS - 1) / BS_THREADS), (sd.sO + jt - 1) / jt);
+    size_t smem = ((size_t)(sd.sI + 1) * jt + sd.sI) * 8;
     u64* d = reinterpret_cast<u64*>(dst);
     const u64* s = reinterpret_cast<const u64*>(src);
     switch (jt) {
-        case 8: basis_switch_kernel<8><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0); break;
-        case 4: basis_switch_kernel<4><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0); break;
-        case 2: basis_switch_kernel<2><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0); break;
-        default: basis_switch_kernel<1><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0); break;
+        case 8: scale_round_kernel<8><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, sd); break;
+        case 4: scale_round_kernel<4><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, sd); break;
+        case 2: scale_round_kernel<2><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, sd); break;
+        default: scale_round_kernel<1><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, sd); break;
     }
     kernel_launch_count_add(1);
     return cudaGetLastError();

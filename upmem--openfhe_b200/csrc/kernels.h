@@ -55,10 +55,21 @@ struct BasisDev {
     const ulonglong2* pre;       // [sq] {[(Q/q_i)^-1]_{q_i} (times an optional scalar), Shoup companion}
     const uint64_t* hat;         // [sq][sp] [Q/q_i]_{p_j}
     const BasisTarget* tgt;      // [sp]
+    const double* qinv;          // [sq] 1./double(q_i)                      (exact form only)
+    const uint64_t* alphaq;      // [sq+1][sp] [alpha*Q]_{p_j}               (exact form only)
+};
+struct ScaleDev {                // DCRTPolyImpl::ScaleAndRound(paramsOutput, ...)
+    uint32_t sI, sO, in0, out0;  // input / output tower counts and their first tower inside [sI+sO]
+    const double* frac;          // [sI]
+    const uint64_t* modo;        // [sO][sI+1]
+    const BasisTarget* tgt;      // [sO] output moduli with their 128-bit Barrett constants
 };
 // dst towers dst0.. of [batch][dstT][N] = ApproxSwitchCRTBasis of src towers src0..src0+sq-1 of [batch][srcT][N]
 cudaError_t launch_basis_switch(const BasisDev& bd, uint64_t* dst, uint32_t dstT, uint32_t dst0, const uint64_t* src,
-                                uint32_t srcT, uint32_t src0, size_t batch, uint32_t logN, cudaStream_t st);
+                                uint32_t srcT, uint32_t src0, size_t batch, uint32_t logN, bool exact, cudaStream_t st);
+// dst [batch][sO][N] = ScaleAndRound of src [batch][sI+sO][N]
+cudaError_t launch_scale_round(const ScaleDev& sd, uint64_t* dst, const uint64_t* src, size_t batch, uint32_t logN,
+                               cudaStream_t st);
 // mode 0: out = (x - v) * c; 1: out = x * c + v; 2: out = (x + v * t) * c, per tower k[i] = {c, c', t, t'};
 // x from [batch][xT][N] (towers 0..l-1), v and out over [batch][l][N]
 cudaError_t launch_tower_affine(int mode, uint64_t* out, const uint64_t* x, const uint64_t* v, size_t batch, uint32_t logN,

@@ -815,6 +815,7 @@ struct fhe_basis {
     void *d_q = nullptr, *d_pre = nullptr, *d_hat = nullptr, *d_tgt = nullptr;
     // ApproxModDown extras: [P^-1]_{q_i} records and the t-folded variant of pre / tgt (cached for the last t)
     void *d_pinv = nullptr, *d_pre_t = nullptr, *d_tgt_t = nullptr;
+    void *d_qinv = nullptr, *d_alphaq = nullptr;   // exact form (SwitchCRTBasis): 1/q_i and [alpha*Q]_{p_j}
     uint64_t t_cached = 0;
     bool pinv_ready = false;
     Scratch s0, s1;
@@ -845,7 +846,7 @@ extern "C" int fhe_basis_destroy(fhe_basis* b) {
     if (!b) return FHE_OK;
     cudaSetDevice(b->ctx->device);
     cudaDeviceSynchronize();
-    for (void* p : {b->d_q, b->d_pre, b->d_hat, b->d_tgt, b->d_pinv, b->d_pre_t, b->d_tgt_t})
+    for (void* p : {b->d_q, b->d_pre, b->d_hat, b->d_tgt, b->d_pinv, b->d_pre_t, b->d_tgt_t, b->d_qinv, b->d_alphaq})
         if (p) b->ctx->arena.release(p);
     b->s0.drop(b->ctx);
     b->s1.drop(b->ctx);
@@ -914,7 +915,7 @@ extern "C" int fhe_approx_switch_crt_basis(fhe_basis* b, fhe_dptr dst, fhe_dptr 
     if (batch == 0) return FHE_OK;
     if (!dst || !src) return fail(FHE_EINVAL, "fhe_approx_switch_crt_basis: null device pointer");
     CUDA_TRY(launch_basis_switch(b->dev, (uint64_t*)(uintptr_t)dst, b->dev.sp, 0, (const uint64_t*)(uintptr_t)src, b->dev.sq, 0,
-                                 batch, b->from->dev.logN, s));
+                                 batch, b->from->dev.logN, false, s));
     return FHE_OK;
 }
 
@@ -950,7 +951,7 @@ extern "C" int fhe_approx_mod_up(fhe_basis* b, fhe_dptr dst_qp, fhe_dptr src_q, 
     // COEFFICIENT form of the Q towers (dcrtpoly-impl.h:1096-1099)
     CUDA_TRY(cudaMemcpyAsync(coef, src, wq * 8, cudaMemcpyDeviceToDevice, s));
     if (format == 0 && (rc = ring_ntt(b->from, coef, batch, true, s, "fhe_approx_mod_up"))) return rc;
-    CUDA_TRY(launch_basis_switch(b->dev, partP, sp, 0, coef, sq, 0, batch, logN, s));          // :1105-1106
+    CUDA_TRY(launch_basis_switch(b->dev, partP, sp, 0, coef, sq, 0, batch, logN, false, s));          // :1105-1106
     if ((rc = ring_ntt(b->to, partP, batch, false, s, "fhe_approx_mod_up"))) return rc;        // :1113-1116
     CUDA_TRY(copy_towers(dst, sq + sp, sq, partP, sp, 0, sp, batch, N, s));
     if (format == 0) {
@@ -1005,7 +1006,7 @@ extern "C" int fhe_approx_mod_down(fhe_basis* b, fhe_dptr dst_q, fhe_dptr src_qp
     uint64_t* sw = (uint64_t*)b->s1.p;
     CUDA_TRY(copy_towers(partP, sp, 0, src, sq + sp, sq, sp, batch, N, s));                    // :1150-1151
     if ((rc = ring_ntt(P, partP, batch, true, s, "fhe_approx_mod_down"))) return rc;
-    CUDA_TRY(launch_basis_switch(bd, sw, sq, 0, partP, sp, 0, batch, logN, s));                // :1152-1159, :1170-1171
+    CUDA_TRY(launch_basis_switch(bd, sw, sq, 0, partP, sp, 0, batch, logN, false, s));                // :1152-1159, :1170-1171
     if ((rc = ring_ntt(Q, sw, batch, false, s, "fhe_approx_mod_down"))) return rc;             // :1172
     CUDA_TRY(launch_tower_affine(0, dst, src, sw, batch, logN, sq, sq + sp, Q->dev.mods,       // :1173
                                  (const ulonglong4*)b->d_pinv, s));
@@ -1132,6 +1133,134 @@ extern "C" int fhe_drop_last_element_and_scale(fhe_rescale* p, fhe_dptr dst, fhe
 extern "C" int fhe_mod_reduce(fhe_rescale* p, fhe_dptr dst, fhe_dptr src, size_t batch, uint64_t t, int format, int stream) {
     if (t == 0) return fail(FHE_EINVAL, "fhe_mod_reduce: t must be positive");
     return rescale_run(p, dst, src, batch, t, format, stream, "fhe_mod_reduce");
+}
+
+// ---- BFV (HPS) set: exact basis switch, ExpandCRTBasis, ScaleAndRound ----------------------------------------
+static int basis_exact_ready(fhe_basis* b) {
+    if (b->dev.qinv) return FHE_OK;
+    const auto& q = b->from->q;
+    const auto& p = b->to->q;
+    std::vector<double> qinv(q.size());
+    for (size_t i = 0; i < q.size(); i++) qinv[i] = 1. / static_cast<double>(q[i]);       // bfvrns-cryptoparameters.cpp:270-273
+    std::vector<uint64_t> aq((q.size() + 1) * p.size());
+    for (size_t j = 0; j < p.size(); j++) {                                                 // :343-350
+        uint64_t Qm = prod_mod(q, (size_t)-1, p[j]);
+        for (size_t a = 0; a <= q.size(); a++) aq[a * p.size() + j] = host::mulmod(Qm, a % p[j], p[j]);
+    }
+    int rc;
+    if ((rc = upload(b->ctx, qinv, &b->d_qinv)) || (rc = upload(b->ctx, aq, &b->d_alphaq))) return rc;
+    b->dev.qinv = (const double*)b->d_qinv;
+    b->dev.alphaq = (const uint64_t*)b->d_alphaq;
+    return FHE_OK;
+}
+
+extern "C" int fhe_switch_crt_basis(fhe_basis* b, fhe_dptr dst, fhe_dptr src, size_t batch, int stream) {
+    if (!b) return fail(FHE_EINVAL, "null basis");
+    cudaStream_t s;
+    int rc = ring_stream(b->from, stream, &s);
+    if (rc) return rc;
+    if (batch == 0) return FHE_OK;
+    if (!dst || !src) return fail(FHE_EINVAL, "fhe_switch_crt_basis: null device pointer");
+    if ((rc = basis_exact_ready(b))) return rc;
+    CUDA_TRY(launch_basis_switch(b->dev, (uint64_t*)(uintptr_t)dst, b->dev.sp, 0, (const uint64_t*)(uintptr_t)src, b->dev.sq, 0,
+                                 batch, b->from->dev.logN, true, s));
+    return FHE_OK;
+}
+
+extern "C" int fhe_expand_crt_basis(fhe_basis* b, fhe_dptr dst_qp, fhe_dptr src_q, size_t batch, int format, int result_format,
+                                    int stream) {
+    if (!b) return fail(FHE_EINVAL, "null basis");
+    cudaStream_t s;
+    int rc = ring_stream(b->from, stream, &s);
+    if (rc) return rc;
+    if ((format != 0 && format != 1) || (result_format != 0 && result_format != 1))
+        return fail(FHE_EINVAL, "fhe_expand_crt_basis: formats must be 0 or 1");
+    if (batch == 0) return FHE_OK;
+    if (!dst_qp || !src_q) return fail(FHE_EINVAL, "fhe_expand_crt_basis: null device pointer");
+    if ((rc = basis_exact_ready(b))) return rc;
+    const uint32_t N = b->from->dev.N, logN = b->from->dev.logN, sq = b->dev.sq, sp = b->dev.sp;
+    uint64_t* dst = (uint64_t*)(uintptr_t)dst_qp;
+    const uint64_t* src = (const uint64_t*)(uintptr_t)src_q;
+    const size_t wq = batch * sq * (size_t)N, wp = batch * sp * (size_t)N;
+    if ((rc = b->s0.need(b->ctx, wq * 8)) || (rc = b->s1.need(b->ctx, wp * 8))) return rc;
+    uint64_t* coef = (uint64_t*)b->s0.p;
+    uint64_t* partP = (uint64_t*)b->s1.p;
+    const char* who = "fhe_expand_crt_basis";
+    CUDA_TRY(cudaMemcpyAsync(coef, src, wq * 8, cudaMemcpyDeviceToDevice, s));
+    if (format == 0 && (rc = ring_ntt(b->from, coef, batch, true, s, who))) return rc;         // dcrtpoly-impl.h:1321-1324
+    CUDA_TRY(launch_basis_switch(b->dev, partP, sp, 0, coef, sq, 0, batch, logN, true, s));    // :1326-1327
+    if (result_format == 0 && (rc = ring_ntt(b->to, partP, batch, false, s, who))) return rc;  // :1338-1341
+    CUDA_TRY(copy_towers(dst, sq + sp, sq, partP, sp, 0, sp, batch, N, s));
+    if (result_format == 0 && format == 0) {
+        CUDA_TRY(copy_towers(dst, sq + sp, 0, src, sq, 0, sq, batch, N, s));                   // :1346-1349
+    } else {
+        if (result_format == 0 && (rc = ring_ntt(b->from, coef, batch, false, s, who))) return rc;   // :1350-1355
+        CUDA_TRY(copy_towers(dst, sq + sp, 0, coef, sq, 0, sq, batch, N, s));                  // COEFFICIENT result keeps coef
+    }
+    return FHE_OK;
+}
+
+struct fhe_scale_round {
+    fhe_ctx* ctx = nullptr;
+    fhe_ring* ring = nullptr;
+    ScaleDev dev{};
+    void *d_frac = nullptr, *d_modo = nullptr, *d_tgt = nullptr;
+};
+
+extern "C" int fhe_scale_round_destroy(fhe_scale_round* p) {
+    if (!p) return FHE_OK;
+    cudaSetDevice(p->ctx->device);
+    cudaDeviceSynchronize();
+    for (void* d : {p->d_frac, p->d_modo, p->d_tgt})
+        if (d) p->ctx->arena.release(d);
+    delete p;
+    return FHE_OK;
+}
+
+extern "C" int fhe_scale_round_create(fhe_ring* ring, uint32_t size_out, int out_last, const double* frac, const uint64_t* modo,
+                                      fhe_scale_round** out) {
+    if (!ring || !frac || !modo || !out) return fail(FHE_EINVAL, "fhe_scale_round_create: null argument");
+    *out = nullptr;
+    const uint32_t T = ring->dev.T;
+    if (size_out == 0 || size_out >= T) return fail(FHE_EINVAL, "fhe_scale_round_create: size_out must be in [1, towers)");
+    const uint32_t sI = T - size_out, sO = size_out;
+    CUDA_TRY(cudaSetDevice(ring->ctx->device));
+    auto* p = new fhe_scale_round;
+    p->ctx = ring->ctx; p->ring = ring;
+    std::vector<double> f(frac, frac + sI);
+    std::vector<uint64_t> m(modo, modo + (size_t)sO * (sI + 1));
+    std::vector<BasisTarget> tgt(sO);
+    const uint32_t out0 = out_last ? sI : 0;
+    for (uint32_t j = 0; j < sO; j++) {
+        BasisTarget g{};
+        g.p = ring->q[out0 + j];
+        if ((g.p & (g.p - 1)) == 0) { delete p; return fail(FHE_EINVAL, "fhe_scale_round_create: output modulus is a power of two"); }
+        unsigned __int128 mu = (~(unsigned __int128)0) / g.p;
+        g.mu_lo = (uint64_t)mu; g.mu_hi = (uint64_t)(mu >> 64);
+        tgt[j] = g;
+    }
+    int rc;
+    if ((rc = upload(p->ctx, f, &p->d_frac)) || (rc = upload(p->ctx, m, &p->d_modo)) || (rc = upload(p->ctx, tgt, &p->d_tgt))) {
+        fhe_scale_round_destroy(p);
+        return rc;
+    }
+    p->dev.sI = sI; p->dev.sO = sO; p->dev.in0 = out_last ? 0 : sO; p->dev.out0 = out0;
+    p->dev.frac = (const double*)p->d_frac;
+    p->dev.modo = (const uint64_t*)p->d_modo;
+    p->dev.tgt = (const BasisTarget*)p->d_tgt;
+    *out = p;
+    return FHE_OK;
+}
+
+extern "C" int fhe_scale_and_round(fhe_scale_round* p, fhe_dptr dst, fhe_dptr src, size_t batch, int stream) {
+    if (!p) return fail(FHE_EINVAL, "null scale-and-round plan");
+    cudaStream_t s;
+    int rc = ring_stream(p->ring, stream, &s);
+    if (rc) return rc;
+    if (batch == 0) return FHE_OK;
+    if (!dst || !src) return fail(FHE_EINVAL, "fhe_scale_and_round: null device pointer");
+    CUDA_TRY(launch_scale_round(p->dev, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, batch, p->ring->dev.logN, s));
+    return FHE_OK;
 }
 
 // ---------------------------------------------------------------------------------------------

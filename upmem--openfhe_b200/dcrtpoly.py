@@ -329,6 +329,14 @@ class Basis:
     def approx_switch(self, dst, src, batch, stream=0):
         N.check(N.lib.fhe_approx_switch_crt_basis(self.h, dst, src, batch, stream))
 
+    def switch_crt_basis(self, dst, src, batch, stream=0):
+        """DCRTPolyImpl::SwitchCRTBasis (dcrtpoly-impl.h:1178-1230), the exact form."""
+        N.check(N.lib.fhe_switch_crt_basis(self.h, dst, src, batch, stream))
+
+    def expand_crt_basis(self, dst_qp, src_q, batch, fmt, result_fmt, stream=0):
+        """self = Q -> P.  DCRTPolyImpl::ExpandCRTBasis (dcrtpoly-impl.h:1311-1358)."""
+        N.check(N.lib.fhe_expand_crt_basis(self.h, dst_qp, src_q, batch, fmt, result_fmt, stream))
+
     def approx_mod_up(self, dst_qp, src_q, batch, fmt, stream=0):
         """self = Q -> P.  DCRTPolyImpl::ApproxModUp (dcrtpoly-impl.h:1085-1133)."""
         N.check(N.lib.fhe_approx_mod_up(self.h, dst_qp, src_q, batch, fmt, stream))
@@ -336,6 +344,29 @@ class Basis:
     def approx_mod_down(self, dst_q, src_qp, batch, t=0, stream=0):
         """self = P -> Q.  DCRTPolyImpl::ApproxModDown (dcrtpoly-impl.h:1136-1175)."""
         N.check(N.lib.fhe_approx_mod_down(self.h, dst_q, src_qp, batch, t, stream))
+
+
+class ScaleRound:
+    """DCRTPolyImpl::ScaleAndRound(paramsOutput, ...) (dcrtpoly-impl.h:1876-1960): `ring` is the input basis, the output
+    moduli are its last (out_last) or first size_out towers; frac / modo are the scheme's tables."""
+
+    def __init__(self, ring, size_out, frac, modo, out_last=True):
+        self.ring, self.size_out = ring, size_out
+        frac, modo = np.ascontiguousarray(frac, np.float64), np.ascontiguousarray(modo, np.uint64)
+        if frac.size != ring.towers - size_out or modo.size != size_out * (ring.towers - size_out + 1):
+            raise ValueError("frac must hold sI values and modo size_out x (sI + 1)")
+        h = ctypes.c_void_p()
+        N.check(N.lib.fhe_scale_round_create(ring.h, size_out, 1 if out_last else 0, frac.ctypes.data, modo.ctypes.data,
+                                             ctypes.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_scale_round_destroy(self.h)
+            self.h = None
+
+    def scale_and_round(self, dst, src, batch, stream=0):
+        N.check(N.lib.fhe_scale_and_round(self.h, dst, src, batch, stream))
 
 
 class Rescale:
