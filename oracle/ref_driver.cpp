@@ -500,6 +500,52 @@ ref_polys* ref_polys_scale_and_round(const ref_polys* a, ref_ctx* Q, ref_ctx* R,
     return r;
 }
 
+// The RNS core of BFVrns EvalMult with multTech == HPS (src/pke/lib/scheme/bfvrns/bfvrns-leveledshe.cpp:193-207,
+// 322-356), on the reference's own DCRTPoly: ExpandCRTBasis of the four input polynomials to QR (EVALUATION), the
+// 2 x 2 tensor product (the plain product loop, :322-334), SetFormat(COEFFICIENT), ScaleAndRound to R, SwitchCRTBasis
+// back to Q.  a0, a1, b0, b1: batches over Q in EVALUATION.  Returns out[0..2] (over Q, COEFFICIENT); 0 on success.
+int ref_bfv_hps_mult(const ref_polys* a0, const ref_polys* a1, const ref_polys* b0, const ref_polys* b1, ref_ctx* R,
+                     ref_ctx* QR, uint64_t t, ref_polys** out) {
+    int rc = 0;
+    std::string err;
+    serial_omp([&] {
+        try {
+            ref_ctx* Q = a0->ctx;
+            auto mq = moduli_of(Q), mr = moduli_of(R);
+            auto ex = make_exact_tables(mq, mr);          // Q -> R
+            auto back = make_exact_tables(mr, mq);        // R -> Q
+            std::vector<double> frac;
+            std::vector<std::vector<NativeInteger>> modr;
+            make_scale_tables(mq, mr, t, frac, modr);
+            for (int k = 0; k < 3; k++) out[k] = new ref_polys{Q, {}};
+            for (size_t i = 0; i < a0->v.size(); i++) {
+                DCRTPoly cv1[2] = {a0->v[i], a1->v[i]}, cv2[2] = {b0->v[i], b1->v[i]};
+                for (auto* cv : {cv1, cv2})
+                    for (int k = 0; k < 2; k++)
+                        cv[k].ExpandCRTBasis(QR->params, R->params, ex.sw.hatInv, ex.sw.hatInvPrecon, ex.hatModpT, ex.alphaQModp,
+                                             ex.sw.mu, ex.qInv, Format::EVALUATION);
+                DCRTPoly cvMult[3];
+                bool first[3] = {true, true, true};
+                for (int x = 0; x < 2; x++)
+                    for (int y = 0; y < 2; y++) {
+                        if (first[x + y]) { cvMult[x + y] = cv1[x] * cv2[y]; first[x + y] = false; }
+                        else cvMult[x + y] += cv1[x] * cv2[y];
+                    }
+                for (int k = 0; k < 3; k++) {
+                    cvMult[k].SetFormat(Format::COEFFICIENT);
+                    cvMult[k] = cvMult[k].ScaleAndRound(R->params, modr, frac, ex.sw.mu);
+                    cvMult[k] = cvMult[k].SwitchCRTBasis(Q->params, back.sw.hatInv, back.sw.hatInvPrecon, back.hatModpT,
+                                                         back.alphaQModp, back.sw.mu, back.qInv);
+                    out[k]->v.push_back(std::move(cvMult[k]));
+                }
+            }
+        }
+        catch (const std::exception& e) { err = e.what(); rc = 1; }
+    });
+    if (rc) g_ref_err = err;
+    return rc;
+}
+
 // mod-ops of the PimData surface executed by the reference's own NativeVector (in-place forms:
 // mubintvecnat.cpp:111-195,370-487, mubintvecnat.h:560-566).  kind = enum mod_kernel.
 // Returns 0, or 1 if the reference threw.

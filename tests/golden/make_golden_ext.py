@@ -109,6 +109,7 @@ def bfv_section(R, O, p):
     R.ref_scale_tables_get.argtypes = [vp, vp, u64, vp, vp]
     R.ref_polys_scale_and_round.restype = vp
     R.ref_polys_scale_and_round.argtypes = [vp, vp, vp, u64]
+    R.ref_bfv_hps_mult.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp)]
     out = []
     for nbits, n, sq, sp, batch, seed, t in BFV_CASES:
         q, psi = np.zeros(sq + sp, np.uint64), np.zeros(sq + sp, np.uint64)
@@ -142,6 +143,20 @@ def bfv_section(R, O, p):
         R.ref_polys_store(hr, p(res))
         rec["sha_scale_round"] = digest(res)
         R.ref_polys_free(hr); R.ref_polys_free(hy)
+        if sq <= 8:      # the composed EvalMult core (bfvrns-leveledshe.cpp:193-207, 322-356) on four seeded inputs
+            ins = [O.fill_ring(batch, n, q[:sq].copy(), seed + 10 + k) for k in range(4)]
+            hs = [R.ref_polys_load(cQ, p(v), batch, 0) for v in ins]
+            outs = (vp * 3)()
+            assert R.ref_bfv_hps_mult(hs[0], hs[1], hs[2], hs[3], cP, cQP, t, outs) == 0
+            rec["sha_mult_in"] = [digest(v) for v in ins]
+            rec["sha_mult_out"] = []
+            for k in range(3):
+                res = np.empty((batch, sq, n), np.uint64)
+                R.ref_polys_store(outs[k], p(res))
+                rec["sha_mult_out"].append(digest(res))
+                R.ref_polys_free(outs[k])
+            for h in hs:
+                R.ref_polys_free(h)
         for c in (cQ, cP, cQP):
             R.ref_ctx_destroy(c)
         out.append(rec)

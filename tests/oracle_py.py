@@ -208,21 +208,41 @@ class OracleBasis:
         return out
 
 
-def _exact_tables(self):
-    qinv, aq = np.empty(self.sq, np.float64), np.empty((self.sq + 1, self.sp), np.uint64)
-    self.o.L.orc_exact_tables(_p(self.Q.q), self.sq, _p(self.P.q), self.sp, _p(qinv), _p(aq))
+def _exact_tables(self, reverse=False):
+    a, b = (self.P, self.Q) if reverse else (self.Q, self.P)
+    qinv, aq = np.empty(len(a.q), np.float64), np.empty((len(a.q) + 1, len(b.q)), np.uint64)
+    self.o.L.orc_exact_tables(_p(a.q), len(a.q), _p(b.q), len(b.q), _p(qinv), _p(aq))
     return qinv, aq
 
 
-def _switch_exact(self, x):
-    hi, hm = self.tables(False)
-    qinv, aq = self.exact_tables()
+def _switch_exact(self, x, reverse=False):
+    a, b = (self.P, self.Q) if reverse else (self.Q, self.P)
+    hi, hm = self.tables(reverse)
+    qinv, aq = self.exact_tables(reverse)
     x = np.ascontiguousarray(x, np.uint64)
-    B = x.size // (self.sq * self.n)
-    out = np.empty((B, self.sp, self.n), np.uint64)
-    self.o.L.orc_switch_crt_basis(_p(out), _p(x), B, self.n, _p(self.Q.q), self.sq, _p(self.P.q), self.sp, _p(hi), _p(hm),
+    B = x.size // (len(a.q) * self.n)
+    out = np.empty((B, len(b.q), self.n), np.uint64)
+    self.o.L.orc_switch_crt_basis(_p(out), _p(x), B, self.n, _p(a.q), len(a.q), _p(b.q), len(b.q), _p(hi), _p(hm),
                                   _p(qinv), _p(aq))
     return out
+
+
+def _bfv_hps_mult(self, a0, a1, b0, b1, frac, modr):
+    """RNS core of BFVrns EvalMult (HPS), bfvrns-leveledshe.cpp:193-207, 322-356: inputs over Q in EVALUATION ->
+    three polynomials over Q in COEFFICIENT."""
+    QP = self.o.ctx(self.n, self.q, self.psi)
+    e = [self.expand(v, 0, 0) for v in (a0, a1, b0, b1)]
+    c0 = QP.elementwise(2, e[0], e[2])
+    c1 = QP.elementwise(0, QP.elementwise(2, e[0], e[3]), QP.elementwise(2, e[1], e[2]))
+    c2 = QP.elementwise(2, e[1], e[3])
+    out = []
+    for c in (c0, c1, c2):
+        r = self.scale_and_round(QP.ntt(c, inverse=True), frac, modr, 1)
+        out.append(self.switch_exact(r, reverse=True))
+    return out
+
+
+OracleBasis.bfv_hps_mult = _bfv_hps_mult
 
 
 def _expand(self, x, fmt, result_fmt):

@@ -267,3 +267,29 @@ def test_scale_and_round_to_first_towers(pkg, backend, oracle):
         o.close()
     d.close()
     ring.close()
+
+
+@pytest.mark.parametrize("case", [c for c in EXT["bfv"] if "sha_mult_out" in c], ids=lambda c: f"N{c['N']}_Q{c['sizeQ']}")
+def test_bfv_hps_mult_core_reference_golden(pkg, backend, oracle, case):
+    """BASELINE configs[4] as a real EvalMult core: ExpandCRTBasis x4 -> tensor product over QR -> INTT -> ScaleAndRound ->
+    SwitchCRTBasis on the device (pkg.BfvHpsMult) against the digests of the reference running the same sequence on its
+    own DCRTPoly (bfvrns-leveledshe.cpp:193-207, 322-356)."""
+    n, sq, sr, batch = case["N"], case["sizeQ"], case["sizeP"], case["batch"]
+    q, psi = np.array(case["q"], np.uint64), np.array(case["psi"], np.uint64)
+    ring = pkg.Ring(backend, n, q, psi)
+    frac = np.array([float.fromhex(v) for v in case["frac_hex"]], np.float64)
+    modr = np.array(case["modr"], np.uint64).reshape(sr, sq + 1)
+    mult = pkg.BfvHpsMult(ring, sq, frac, modr)
+    ins = [oracle.fill_ring(batch, n, q[:sq].copy(), case["seed"] + 10 + k) for k in range(4)]
+    d = Dev(backend)
+    din = [d.put(v) for v in ins]
+    dout = [d.new(batch * sq * n) for _ in range(3)]
+    for _ in range(2):                                  # twice: scratch buffers and cached tables are reused
+        mult(dout, din[0:2], din[2:4], batch)
+        got = [backend.d2h(p_, batch * sq * n) for p_ in dout]
+        assert [digest(v) for v in got] == case["sha_mult_out"]
+    for v, dv in zip(ins, din):
+        assert np.array_equal(backend.d2h(dv, v.size).reshape(v.shape), v), "inputs modified"
+    mult.close()
+    d.close()
+    ring.close()

@@ -48,6 +48,7 @@ def ref():
     R.ref_scale_tables_get.argtypes = [vp, vp, u64, vp, vp]
     R.ref_polys_scale_and_round.restype = vp
     R.ref_polys_scale_and_round.argtypes = [vp, vp, vp, u64]
+    R.ref_bfv_hps_mult.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp)]
     return R
 
 
@@ -224,4 +225,31 @@ def test_bfv_hps_set_matches_reference(oracle, ref, nbits, n, sq, sp, t):
     assert np.array_equal(res, ob.scale_and_round(y, frac, modr, 1))
     ref.ref_polys_free(hr); ref.ref_polys_free(hy)
     for c in (cQ, cP, cQP):
+        ref.ref_ctx_destroy(c)
+
+
+@pytest.mark.parametrize("nbits,n,sq,sr,t", [(30, 16, 2, 3, 65537), (60, 256, 3, 4, 65537), (60, 1 << 11, 4, 5, 786433)])
+def test_bfv_hps_mult_core_matches_reference(oracle, ref, nbits, n, sq, sr, t):
+    """The RNS core of BFVrns EvalMult (HPS), bfvrns-leveledshe.cpp:193-207, 322-356, executed by the reference's own
+    DCRTPoly vs the composition of the restated pieces."""
+    q, psi = oracle.gen_params(nbits, n, sq + sr)
+    ob = oracle.basis(n, q, psi, sq)
+    mk = lambda a, b: ref.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+    cQ, cR, cQR = mk(0, sq), mk(sq, sq + sr), mk(0, sq + sr)
+    B = 2
+    ins = [oracle.fill_ring(B, n, q[:sq].copy(), 90 + k) for k in range(4)]
+    hs = [ref.ref_polys_load(cQ, p(v), B, 0) for v in ins]
+    outs = (vp * 3)()
+    assert ref.ref_bfv_hps_mult(hs[0], hs[1], hs[2], hs[3], cR, cQR, t, outs) == 0, ref.ref_last_error()
+    frac, modr = np.empty(sq, np.float64), np.empty((sr, sq + 1), np.uint64)
+    ref.ref_scale_tables_get(cQ, cR, t, p(frac), p(modr))
+    want = ob.bfv_hps_mult(ins[0], ins[1], ins[2], ins[3], frac, modr)
+    for k in range(3):
+        res = np.empty((B, sq, n), np.uint64)
+        ref.ref_polys_store(outs[k], p(res))
+        assert np.array_equal(res, want[k]), f"c{k}"
+        ref.ref_polys_free(outs[k])
+    for h in hs:
+        ref.ref_polys_free(h)
+    for c in (cQ, cR, cQR):
         ref.ref_ctx_destroy(c)

@@ -395,3 +395,47 @@ class Rescale:
 
     def mod_reduce(self, dst, src, batch, t, fmt, stream=0):
         N.check(N.lib.fhe_mod_reduce(self.h, dst, src, batch, t, fmt, stream))
+
+
+class BfvHpsMult:
+    """The RNS core of BFVrns EvalMult with the HPS technique (src/pke/lib/scheme/bfvrns/bfvrns-leveledshe.cpp:193-207,
+    322-356) composed from the device calls: ExpandCRTBasis of the four input polynomials Q -> QR, the fused 2 x 2 tensor
+    product over QR, inverse NTT, ScaleAndRound QR -> R, SwitchCRTBasis R -> Q.  `ring_qr` holds the Q towers followed by
+    the R towers; frac / modr are the scheme's t*R/(Q*R) tables (bfvrns-cryptoparameters.cpp:278-311).
+    Inputs: a = (a0, a1), b = (b0, b1) device addresses over Q in EVALUATION; outputs c = (c0, c1, c2) over Q in COEFFICIENT."""
+
+    def __init__(self, ring_qr, size_q, frac, modr):
+        self.ring = ring_qr
+        self.sq, self.sr = size_q, ring_qr.towers - size_q
+        self.rq, self.rr = RingView(ring_qr, 0, size_q), RingView(ring_qr, size_q, self.sr)
+        self.q2r, self.r2q = Basis(self.rq, self.rr), Basis(self.rr, self.rq)
+        self.scale = ScaleRound(ring_qr, self.sr, frac, modr, out_last=True)
+        self.batch, self.bufs = 0, []
+
+    def _reserve(self, batch):
+        if batch <= self.batch:
+            return
+        be = self.ring.be
+        for p in self.bufs:
+            be.free(p)
+        wqr = self.ring.words(batch) * 8
+        self.bufs = [be.alloc(wqr) for _ in range(7)] + [be.alloc(self.rr.words(batch) * 8)]
+        self.batch = batch
+
+    def __call__(self, c, a, b, batch, stream=0):
+        self._reserve(batch)
+        e, t, r = self.bufs[0:4], self.bufs[4:7], self.bufs[7]
+        for dst, src in zip(e, (a[0], a[1], b[0], b[1])):
+            self.q2r.expand_crt_basis(dst, src, batch, EVALUATION, EVALUATION, stream)
+        self.ring.ct_multiply(t, e[0:2], e[2:4], batch, 0, stream)
+        for k in range(3):
+            self.ring.ntt(t[k], batch, inverse=True, stream=stream)
+            self.scale.scale_and_round(r, t[k], batch, stream)
+            self.r2q.switch_crt_basis(c[k], r, batch, stream)
+
+    def close(self):
+        for p in self.bufs:
+            self.ring.be.free(p)
+        self.bufs, self.batch = [], 0
+        for o in (self.scale, self.q2r, self.r2q, self.rq, self.rr):
+            o.close()
