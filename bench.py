@@ -453,6 +453,26 @@ def ntt_extra(pkg, be):
         for b_ in (dq, dp, dqp, dr):
             be.free(b_)
         ring.close()
+        # BFVrns EvalMult core with the HPS technique (BASELINE configs[4] as a real EvalMult): Q = 16 towers, R = 17,
+        # N = 2^15; per ciphertext pair: 4 ExpandCRTBasis, tensor product over QR, 3 x (INTT, ScaleAndRound, SwitchCRTBasis)
+        n, sq, sr, batch = 1 << 15, 16, 17, 32
+        q, psi = pkg.gen_params(60, n, sq + sr)
+        ring = pkg.Ring(be, n, q, psi)
+        frac, modr = pkg.hps_scale_tables(q[:sq], q[sq:], 65537)
+        mult = pkg.BfvHpsMult(ring, sq, frac, modr)
+        wq = batch * sq * n
+        ins = [be.alloc(wq * 8) for _ in range(4)]
+        outs = [be.alloc(wq * 8) for _ in range(3)]
+        for i, p_ in enumerate(ins):
+            mult.rq.fill_uniform(p_, batch, 20260040 + i)
+        ms = timed(lambda: mult(outs, ins[0:2], ins[2:4], batch), reps=3)
+        out["bfv_hps_evalmult_core_n32768_q16_r17_b32"] = {
+            "ms": ms, "ciphertext_products_per_s": batch / (ms * 1e-3),
+            "note": "ExpandCRTBasis x4 -> tensor product over QR -> INTT -> ScaleAndRound -> SwitchCRTBasis, device-resident"}
+        mult.close()
+        for p_ in ins + outs:
+            be.free(p_)
+        ring.close()
     except Exception as ex:
         out["error"] = str(ex)[:300]
     return out

@@ -121,6 +121,31 @@ private:
   fhe_rescale *plan_ = nullptr;
 };
 
+/* Tables of DCRTPolyImpl::ScaleAndRound(paramsOutput, ...) (dcrtpoly-impl.h:1876-1960): `ring` is the input basis, the
+ * output basis its last (outLast) or first sizeOut towers; frac / modo are the scheme's tOSHatInvModsDivsFrac /
+ * tOSHatInvModsDivsModo (row-major [sizeOut][sizeIn+1], bfvrns-cryptoparameters.cpp:278-311). */
+class PimScaleRound {
+public:
+  PimScaleRound(std::shared_ptr<PimRing> ring, uint32_t sizeOut, bool outLast, const std::vector<double> &frac,
+                const std::vector<uint64_t> &modo)
+      : ring_(std::move(ring)),
+        out_(PimRing::View(ring_, outLast ? (uint32_t)ring_->GetNumTowers() - sizeOut : 0, sizeOut)) {
+    if (frac.size() != ring_->GetNumTowers() - sizeOut || modo.size() != (size_t)sizeOut * (frac.size() + 1))
+      throw pim_math_error("PimScaleRound: table sizes do not match the bases");
+    PimManager::check(fhe_scale_round_create(ring_->handle(), sizeOut, outLast ? 1 : 0, frac.data(), modo.data(), &plan_),
+                      "PimScaleRound");
+  }
+  ~PimScaleRound() { fhe_scale_round_destroy(plan_); }
+  PimScaleRound(const PimScaleRound &) = delete;
+  PimScaleRound &operator=(const PimScaleRound &) = delete;
+  fhe_scale_round *handle() const { return plan_; }
+  const std::shared_ptr<PimRing> &Out() const { return out_; }
+
+private:
+  std::shared_ptr<PimRing> ring_, out_;
+  fhe_scale_round *plan_ = nullptr;
+};
+
 class PimDCRTPoly {
 public:
   PimDCRTPoly(std::shared_ptr<PimRing> ring, size_t batch, PimFormat format, const uint64_t *host = nullptr,
@@ -213,6 +238,25 @@ public:
     if (format_ != PIM_EVALUATION) throw pim_not_implemented_error("ApproxModDown expects Format::EVALUATION");
     PimDCRTPoly out(pToQ.To(), batch_, PIM_EVALUATION, nullptr, stream_);
     PimManager::check(fhe_approx_mod_down(pToQ.handle(), out.d_, d_, batch_, t, stream_), "ApproxModDown");
+    return out;
+  }
+  /* dcrtpoly-impl.h:1178-1230: the exact switch (BFV) */
+  PimDCRTPoly SwitchCRTBasis(const PimBasis &basis) const {
+    PimDCRTPoly out(basis.To(), batch_, format_, nullptr, stream_);
+    PimManager::check(fhe_switch_crt_basis(basis.handle(), out.d_, d_, batch_, stream_), "SwitchCRTBasis");
+    return out;
+  }
+  /* dcrtpoly-impl.h:1311-1358 (in place in the reference) */
+  PimDCRTPoly ExpandCRTBasis(const PimBasis &qToP, const std::shared_ptr<PimRing> &ringQP, PimFormat resultFormat) const {
+    PimDCRTPoly out(ringQP, batch_, resultFormat, nullptr, stream_);
+    PimManager::check(fhe_expand_crt_basis(qToP.handle(), out.d_, d_, batch_, (int)format_, (int)resultFormat, stream_),
+                      "ExpandCRTBasis");
+    return out;
+  }
+  /* dcrtpoly-impl.h:1876-1960 */
+  PimDCRTPoly ScaleAndRound(const PimScaleRound &plan) const {
+    PimDCRTPoly out(plan.Out(), batch_, format_, nullptr, stream_);
+    PimManager::check(fhe_scale_and_round(plan.handle(), out.d_, d_, batch_, stream_), "ScaleAndRound");
     return out;
   }
   /* dcrtpoly-impl.h:746-769 (in place in the reference).  As there, a COEFFICIENT input comes back with forward-

@@ -183,6 +183,22 @@ static void test_dcrtpoly_ext(uint32_t N, uint32_t sq, uint32_t sp, size_t B) {
     orc_switch_tables(q.data(), sq, q.data() + sq, sp, hi.data(), hm.data());
     orc_approx_switch(e4.data(), coef.data(), B, N, q.data(), sq, q.data() + sq, sp, hi.data(), hm.data());
     EXPECT(xc.ApproxSwitchCRTBasis(qToP).GetValues() == e4, "ApproxSwitchCRTBasis N=%u", N);
+    // BFV (HPS) set
+    std::vector<double> qinv(sq);
+    std::vector<uint64_t> aq((size_t)(sq + 1) * sp), e5(B * sp * (size_t)N);
+    orc_exact_tables(q.data(), sq, q.data() + sq, sp, qinv.data(), aq.data());
+    orc_switch_crt_basis(e5.data(), coef.data(), B, N, q.data(), sq, q.data() + sq, sp, hi.data(), hm.data(), qinv.data(), aq.data());
+    EXPECT(xc.SwitchCRTBasis(qToP).GetValues() == e5, "SwitchCRTBasis N=%u", N);
+    orc_expand_crt_basis(oQ, oP, exp.data(), hx.data(), B, 0, 1);
+    PimDCRTPoly ex = x.ExpandCRTBasis(qToP, ring, PIM_COEFFICIENT);
+    EXPECT(ex.GetFormat() == PIM_COEFFICIENT && ex.GetValues() == exp, "ExpandCRTBasis N=%u", N);
+    std::vector<double> frac(sq);
+    std::vector<uint64_t> modo((size_t)sp * (sq + 1)), e6(B * sp * (size_t)N);
+    for (uint32_t i = 0; i < sq; i++) frac[i] = (double)(i + 1) / (sq + 2.5);
+    for (size_t k = 0; k < modo.size(); k++) modo[k] = orc_uniform_at(99, k, q[sq + k / (sq + 1)]);
+    orc_scale_and_round(e6.data(), hy.data(), B, N, sq, q.data() + sq, sp, 1, frac.data(), modo.data());
+    PimScaleRound sr(ring, sp, true, frac, modo);
+    EXPECT(y.ScaleAndRound(sr).GetValues() == e6, "ScaleAndRound N=%u", N);
     for (orc_ctx* c : {oQP, oQ, oP, oR, oL}) orc_ctx_destroy(c);
 }
 

@@ -87,3 +87,19 @@ def test_cpp_surface_builds_and_fails_loudly_without_gpu():
         pytest.skip("a GPU is present: the binary is run by the gpu tests")
     r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert r.returncode != 0 and "no CPU fallback" in r.stdout
+
+
+def test_hps_scale_tables_equal_the_reference():
+    """Host-side table recipe (no GPU needed): equals the tables the reference's BigInteger code produced
+    (tests/golden/ext_vectors.json, written by tests/golden/make_golden_ext.py from the compiled reference)."""
+    import importlib
+    import json
+    import numpy as np
+    pkg = importlib.import_module("upmem--openfhe_b200")
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ext_vectors.json")) as f:
+        cases = json.load(f)["bfv"]
+    for c in cases:
+        sq = c["sizeQ"]
+        frac, modr = pkg.hps_scale_tables(c["q"][:sq], c["q"][sq:], c["t"])
+        assert [float(v).hex() for v in frac] == c["frac_hex"]
+        assert modr.reshape(-1).tolist() == c["modr"]

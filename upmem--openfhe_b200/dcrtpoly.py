@@ -439,3 +439,24 @@ class BfvHpsMult:
         self.bufs, self.batch = [], 0
         for o in (self.scale, self.q2r, self.r2q, self.rq, self.rr):
             o.close()
+
+
+def hps_scale_tables(q, r, t):
+    """The ScaleAndRound tables of the HPS multiplication, t*R/(Q*R) from QR down to R, as
+    src/pke/lib/scheme/bfvrns/bfvrns-cryptoparameters.cpp:278-311 computes them (BigInteger there, Python integers
+    here): frac[i] = double([(QR/q_i)^-1 * R * t]_{q_i}) / double(q_i);
+    modr[j][i] = floor(t * R * [(QR/q_i)^-1]_{q_i} / q_i) mod r_j, modr[j][sizeQ] the same with r_j in place of q_i."""
+    q, r = [int(v) for v in q], [int(v) for v in r]
+    R = 1
+    for v in r:
+        R *= v
+    QR = R
+    for v in q:
+        QR *= v
+    frac = np.array([float((pow(QR // qi, -1, qi) * R * t) % qi) / float(qi) for qi in q], np.float64)
+    modr = np.empty((len(r), len(q) + 1), np.uint64)
+    for j, rj in enumerate(r):
+        for i, qi in enumerate(q):
+            modr[j, i] = ((t * R * pow(QR // qi, -1, qi)) // qi) % rj
+        modr[j, len(q)] = ((t * R * pow(QR // rj, -1, rj)) // rj) % rj
+    return frac, modr
