@@ -307,6 +307,13 @@ def main():
             med = statistics.median(r["step_seconds"])
             cpu = {"value": r["coeff_ops_per_step"] / med, "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
                    "sample": f"full batch {BATCH} (same workload), in-place += and *=, omp-for over the batch, median of 5"}
+            if not args.no_extra:     # the reference's own SwitchFormat on the host cores, beside the NTT figure
+                rn = cpu_baseline.time_ntt(1 << 16, 30, 16, NBITS, steps=3, warmup=1)
+                mn = statistics.median(rn["step_seconds"])
+                if "ntt_n65536_t30_b64" in extra:
+                    extra["ntt_n65536_t30_b64"]["cpu_reference"] = {
+                        "coeff_per_s": rn["coeff_ops_per_step"] / mn, "cores": rn["cores"], "kind": rn["kind"],
+                        "sample": "batch 16 of the same ring, forward + inverse SwitchFormat, omp-for over the batch, median of 3"}
         except Exception as ex:      # the checker is optional for the product, never the other way round
             cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": str(ex)[:200]}
 

@@ -137,3 +137,43 @@ def test_device_checksum_matches_host(pkg, backend):
     assert backend.checksum(p, x.size) == sh.checksum(x)
     assert backend.checksum(p, 0) == (0, 0)
     backend.free(p)
+
+
+def test_concurrent_callers_on_different_streams(pkg, backend, oracle):
+    """SURVEY §8(b) "Threading": the reference's callers are OpenMP loops, so the C ABI must accept concurrent calls on
+    different buffers (locked arena, per-call stream).  Eight threads allocate, run add / mul / NTT round trips on their
+    own stream index and free; every result is checked."""
+    import threading
+    n, towers, batch = 1 << 12, 3, 4
+    q, psi = oracle.gen_params(60, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q, psi)
+    nstreams = pkg._native.lib.fhe_num_streams(backend.h)
+    errors = []
+
+    def worker(tid):
+        try:
+            st = tid % nstreams
+            for rep in range(6):
+                a = oracle.fill_ring(batch, n, q, 100 + 10 * tid + rep)
+                b = oracle.fill_ring(batch, n, q, 500 + 10 * tid + rep)
+                da = pkg.DCRTPolyBatch(ring, batch, pkg.EVALUATION, a, stream=st)
+                db = pkg.DCRTPolyBatch(ring, batch, pkg.EVALUATION, b, stream=st)
+                dc = da * db
+                dc += da
+                dc.SwitchFormat()
+                dc.SwitchFormat()
+                want = octx.elementwise(0, octx.elementwise(2, a, b), a)
+                if not np.array_equal(dc.to_host(), want):
+                    errors.append((tid, rep))
+                del da, db, dc
+        except Exception as ex:                       # noqa: BLE001
+            errors.append((tid, repr(ex)))
+
+    threads = [threading.Thread(target=worker, args=(t,)) for t in range(8)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    ring.close()
