@@ -238,6 +238,134 @@ inline bool resident_switch_format(PimManager *pim, const Towers &a, std::shared
   return true;
 }
 
+/* ---- the neighbouring DCRTPoly methods on resident operands -----------------------
+ * Plans (basis tables, rescale constants) are cached per pair of rings, like the schemes' per-parameter-set tables;
+ * a plan owns scratch buffers, so a call holds its mutex while it enqueues work (everything runs on stream 0). */
+struct PlanLock {
+  std::mutex mu;
+};
+template <class Plan>
+struct CachedPlan {
+  std::shared_ptr<Plan> plan;
+  std::shared_ptr<PlanLock> lock = std::make_shared<PlanLock>();
+};
+
+inline CachedPlan<PimBasis> basis_for(const std::shared_ptr<PimRing> &from, const std::shared_ptr<PimRing> &to) {
+  static std::mutex mu;
+  static std::map<std::pair<PimRing *, PimRing *>, CachedPlan<PimBasis>> cache;
+  std::lock_guard<std::mutex> lock(mu);
+  auto key = std::make_pair(from.get(), to.get());
+  auto it = cache.find(key);
+  if (it != cache.end()) return it->second;
+  CachedPlan<PimBasis> c;
+  c.plan = std::make_shared<PimBasis>(from, to);        /* tables derived from the moduli = the schemes' values */
+  cache.emplace(key, c);
+  return c;
+}
+
+inline CachedPlan<PimRescale> rescale_for(const std::shared_ptr<PimRing> &ring) {
+  static std::mutex mu;
+  static std::map<PimRing *, CachedPlan<PimRescale>> cache;
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(ring.get());
+  if (it != cache.end()) return it->second;
+  CachedPlan<PimRescale> c;
+  c.plan = std::make_shared<PimRescale>(ring);
+  cache.emplace(ring.get(), c);
+  return c;
+}
+
+/* a fresh device copy shaped like `towers` (which only have to carry the right moduli, roots and lengths) */
+template <class Towers>
+inline std::shared_ptr<Resident> new_resident(PimManager *pim, const Towers &towers) {
+  auto r = std::make_shared<Resident>();
+  r->ring = ring_of(pim, towers);
+  r->ctx = pim->context();
+  r->towers = towers.size();
+  r->n = towers[0].GetRingDimension();
+  PimManager::check(fhe_alloc(r->ctx, r->towers * r->n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
+  r->device_newer = true;
+  return r;
+}
+
+/* DCRTPolyImpl::AutomorphismTransform (dcrtpoly-impl.h:348-369): out = sigma_k(a); format 0 EVALUATION, 1 COEFFICIENT */
+template <class Towers>
+inline bool resident_automorphism(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
+                                  std::shared_ptr<Resident> &rout, uint32_t k, int format) {
+  if (!pim || a.empty() || out.size() != a.size()) return false;
+  auto da = ensure_device(pim, a, ra);
+  auto r = new_resident(pim, out);
+  PimManager::check(fhe_automorphism(da->ring->handle(), r->d, da->d, 1, k, format, 0), "pim hook: automorphism");
+  rout = r;
+  return true;
+}
+
+/* DCRTPolyImpl::DropLastElementAndScale (dcrtpoly-impl.h:746-769), EVALUATION input: `rest` = the towers that
+ * remain (the caller has already shrunk its host tower vector); the device copy is replaced by the rescaled one. */
+template <class Towers>
+inline bool resident_rescale(PimManager *pim, const std::shared_ptr<Resident> &full, const Towers &rest,
+                             std::shared_ptr<Resident> &res) {
+  auto plan = rescale_for(full->ring);
+  auto r = new_resident(pim, rest);
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_drop_last_element_and_scale(plan.plan->handle(), r->d, full->d, 1, 0, 0), "pim hook: rescale");
+  }
+  res = r;      /* the old device copy is released when `full` goes out of scope; stream order keeps it valid until then */
+  return true;
+}
+
+/* DCRTPolyImpl::ApproxSwitchCRTBasis (dcrtpoly-impl.h:1034-1082): a over its first `sq` towers -> out over its own moduli */
+template <class Towers>
+inline bool resident_approx_switch(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, size_t sq, const Towers &out,
+                                   std::shared_ptr<Resident> &rout) {
+  if (!pim || a.empty() || out.empty() || sq != a.size()) return false;      /* partial source bases stay on the CPU path */
+  auto da = ensure_device(pim, a, ra);
+  auto r = new_resident(pim, out);
+  auto plan = basis_for(da->ring, r->ring);
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_approx_switch_crt_basis(plan.plan->handle(), r->d, da->d, 1, 0), "pim hook: basis switch");
+  }
+  rout = r;
+  return true;
+}
+
+/* DCRTPolyImpl::ApproxModDown (dcrtpoly-impl.h:1136-1175), EVALUATION input over QP: out over the first `sq` towers */
+template <class Towers>
+inline bool resident_mod_down(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, size_t sq, uint64_t t,
+                              const Towers &out, std::shared_ptr<Resident> &rout) {
+  if (!pim || a.empty() || sq == 0 || sq >= a.size() || out.size() != sq) return false;
+  auto da = ensure_device(pim, a, ra);
+  static std::mutex mu;
+  static std::map<std::pair<PimRing *, size_t>, std::pair<std::shared_ptr<PimRing>, std::shared_ptr<PimRing>>> views;
+  std::shared_ptr<PimRing> rq, rp;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto key = std::make_pair(da->ring.get(), sq);
+    auto it = views.find(key);
+    if (it == views.end())
+      it = views.emplace(key, std::make_pair(PimRing::View(da->ring, 0, (uint32_t)sq),
+                                             PimRing::View(da->ring, (uint32_t)sq, (uint32_t)(a.size() - sq)))).first;
+    rq = it->second.first;
+    rp = it->second.second;
+  }
+  auto r = std::make_shared<Resident>();
+  r->ring = rq;
+  r->ctx = pim->context();
+  r->towers = sq;
+  r->n = da->n;
+  PimManager::check(fhe_alloc(r->ctx, r->towers * r->n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
+  r->device_newer = true;
+  auto plan = basis_for(rp, rq);
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_approx_mod_down(plan.plan->handle(), r->d, da->d, 1, t, 0), "pim hook: mod down");
+  }
+  rout = r;
+  return true;
+}
+
 }  // namespace pimhook
 
 #endif /* _PIM_HOOK_ */

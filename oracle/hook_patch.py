@@ -140,6 +140,58 @@ def patch_impl(text):
                 "            return;\n"
                 "        }\n"
                 "    }", rel)
+    # ---- the neighbouring methods: same pattern, device forms of csrc/automorph.cu and
+    # csrc/basis.cu.  Each hook leaves the reference's own checks / exceptions to the CPU path (odd index, formats).
+    auto_hook = ("\n    if (pim && (i & 1)%s) {\n"
+                 "        DCRTPolyImpl<VecType> dev(m_params, m_format, true);\n"
+                 "        if (pimhook::resident_automorphism(pim.get(), m_vectors_, pimres_, dev.m_vectors_, dev.pimres_, i,\n"
+                 "                                           m_format == Format::EVALUATION ? 0 : 1)) {\n"
+                 "            dev.pim = pim;\n"
+                 "            return dev;\n"
+                 "        }\n"
+                 "    }")
+    sig = "DCRTPolyImpl<VecType> DCRTPolyImpl<VecType>::AutomorphismTransform(uint32_t i) const {"
+    text = once(text, sig, sig + auto_hook % "", rel)
+    sig = "DCRTPolyImpl<VecType> DCRTPolyImpl<VecType>::AutomorphismTransform(uint32_t i, const std::vector<uint32_t>& vec) const {"
+    text = once(text, sig, sig + auto_hook % " && m_format == Format::EVALUATION", rel)
+    # DropLastElementAndScale, EVALUATION input: shrink the host tower vector and the parameters exactly as
+    # DropLastElement (dcrtpoly-impl.h:719-728) does, without touching the (stale) host values
+    sig = "                                                    const std::vector<NativeInteger>& qlInvModqPrecon) {\n    // TODO: move this inside loop if omp enabled\n    auto lastPoly(m_vectors.back());"
+    text = once(text, sig,
+                "                                                    const std::vector<NativeInteger>& qlInvModqPrecon) {\n"
+                "    if (pim && m_format == Format::EVALUATION && m_vectors_.size() > 1) {\n"
+                "        auto full = pimhook::ensure_device(pim.get(), m_vectors_, pimres_);\n"
+                "        m_vectors_.resize(m_vectors_.size() - 1);\n"
+                "        DCRTPolyImpl::Params* newP = new DCRTPolyImpl::Params(*m_params);\n"
+                "        newP->PopLastParam();\n"
+                "        m_params.reset(newP);\n"
+                "        pimres_.reset();\n"
+                "        pimhook::resident_rescale(pim.get(), full, m_vectors_, pimres_);\n"
+                "        return;\n"
+                "    }\n"
+                "    // TODO: move this inside loop if omp enabled\n    auto lastPoly(m_vectors.back());", rel)
+    # ApproxSwitchCRTBasis (const, returns a polynomial over paramsP)
+    sig = ("    const std::vector<std::vector<NativeInteger>>& QHatModp, const std::vector<DoubleNativeInt>& modpBarrettMu) const {\n"
+           "#if defined(HAVE_INT128) && NATIVEINT == 64\n    DCRTPolyImpl<VecType> ans(paramsP, m_format, true);\n")
+    text = once(text, sig, sig +
+                "    if (pim && m_vectors_.size() <= paramsQ->GetParams().size() &&\n"
+                "        pimhook::resident_approx_switch(pim.get(), m_vectors_, pimres_, m_vectors_.size(), ans.m_vectors_, ans.pimres_)) {\n"
+                "        ans.pim = pim;\n"
+                "        return ans;\n"
+                "    }\n", rel)
+    # ApproxModDown (const, EVALUATION input over QP, returns a polynomial over Q)
+    sig = ("    usint sizeQP = m_vectors.size();\n    usint sizeP  = paramsP->GetParams().size();\n    usint sizeQ  = sizeQP - sizeP;\n")
+    text = once(text, sig,
+                "    if (pim && m_format == Format::EVALUATION && m_vectors_.size() > paramsP->GetParams().size()) {\n"
+                "        usint devQ = m_vectors_.size() - paramsP->GetParams().size();\n"
+                "        DCRTPolyImpl<VecType> dev(paramsQ, Format::EVALUATION, true);\n"
+                "        if (paramsQ->GetParams().size() > devQ)\n"
+                "            dev.DropLastElements(paramsQ->GetParams().size() - devQ);\n"
+                "        if (pimhook::resident_mod_down(pim.get(), m_vectors_, pimres_, devQ, t.ConvertToInt(), dev.m_vectors_, dev.pimres_)) {\n"
+                "            dev.pim = pim;\n"
+                "            return dev;\n"
+                "        }\n"
+                "    }\n" + sig, rel)
     head, sep, tail = text.partition("namespace lbcrypto {")
     return head + "#define m_vectors PimHostVectors()\n" + sep + tail + "\n#undef m_vectors\n"
 

@@ -39,6 +39,10 @@ def hooked():
     H.ref_polys_rescale.argtypes = [vp, vp, u64]
     H.ref_polys_binary.restype = vp
     H.ref_polys_binary.argtypes = [vp, vp, ci]
+    H.ref_polys_approx_switch.restype = vp
+    H.ref_polys_approx_switch.argtypes = [vp, vp]
+    H.ref_polys_approx_mod_down.restype = vp
+    H.ref_polys_approx_mod_down.argtypes = [vp, vp, vp, u64]
     return H
 
 
@@ -199,3 +203,49 @@ def test_resident_out_of_place_operators(hooked, oracle, pkg):
     for h in (ha, hb, h1, h2, h3):
         H.ref_polys_free(h)
     H.ref_ctx_destroy(ctx)
+
+
+@pytest.mark.gpu
+def test_resident_neighbouring_methods(hooked, oracle, pkg):
+    """AutomorphismTransform, DropLastElementAndScale, ApproxSwitchCRTBasis and ApproxModDown of the reference's own
+    DCRTPoly with the handle attached (SURVEY §8(f) ranks 3, 4 through the live intercept): a CKKS-like chain
+    a *= b; sigma_5; ModDown; rescale stays on the device until the result is read, and equals the CPU path."""
+    H = hooked
+    n, sq, sp, batch = 1 << 12, 4, 2, 2
+    q, psi = oracle.gen_params(60, n, sq + sp)
+    ob = oracle.basis(n, q, psi, sq)
+    oQP = oracle.ctx(n, q, psi)
+    mk = lambda a, b: H.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+    cQ, cP, cQP, cRest = mk(0, sq), mk(sq, sq + sp), mk(0, sq + sp), mk(0, sq - 1)
+    a, b = oracle.fill_ring(batch, n, q, 61), oracle.fill_ring(batch, n, q, 62)
+    ha, hb = H.ref_polys_load(cQP, p(a), batch, 0), H.ref_polys_load(cQP, p(b), batch, 0)
+    assert H.ref_polys_set_pim(ha, 1) == 0, H.ref_last_error()
+    up0, down0 = counters(H)
+    launches0 = pkg._native.lib.fhe_launch_count()
+    assert H.ref_polys_op(ha, hb, 2, 1) >= 0                               # a *= b over QP
+    h1 = H.ref_polys_automorphism(ha, 5, 0)                                # sigma_5 (result carries the handle)
+    assert h1, H.ref_last_error()
+    h2 = H.ref_polys_approx_mod_down(h1, cQ, cP, 0)                        # QP -> Q
+    assert h2, H.ref_last_error()
+    assert H.ref_polys_rescale(h2, cRest, 0) == 0, H.ref_last_error()      # drop the last tower of Q and scale
+    assert counters(H) == (up0 + 2 * batch, down0), "nothing may be downloaded before the result is read"
+    assert pkg._native.lib.fhe_launch_count() - launches0 >= 4 * batch
+    want = oracle.rescale(n, q[:sq].copy(), psi[:sq].copy(), ob.mod_down(oQP.automorphism(oQP.elementwise(2, a, b), 5, 0), 0), 0, 0)
+    res = np.empty((batch, sq - 1, n), np.uint64)
+    H.ref_polys_store(h2, p(res))
+    assert np.array_equal(res, want)
+    assert counters(H) == (up0 + 2 * batch, down0 + batch)
+    # ApproxSwitchCRTBasis Q -> P on a resident operand in COEFFICIENT format
+    x = oracle.fill_ring(batch, n, q[:sq].copy(), 63)
+    hx = H.ref_polys_load(cQ, p(x), batch, 1)
+    assert H.ref_polys_set_pim(hx, 1) == 0
+    hs = H.ref_polys_approx_switch(hx, cP)
+    res2 = np.empty((batch, sp, n), np.uint64)
+    H.ref_polys_store(hs, p(res2))
+    assert np.array_equal(res2, ob.approx_switch(x))
+    # an even automorphism index still raises the reference's own error
+    assert not H.ref_polys_automorphism(ha, 4, 0) and b"not odd" in H.ref_last_error()
+    for h in (ha, hb, h1, h2, hx, hs):
+        H.ref_polys_free(h)
+    for c in (cQ, cP, cQP, cRest):
+        H.ref_ctx_destroy(c)
