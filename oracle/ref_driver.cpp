@@ -504,11 +504,34 @@ ref_polys* ref_polys_scale_and_round(const ref_polys* a, ref_ctx* Q, ref_ctx* R,
 // 322-356), on the reference's own DCRTPoly: ExpandCRTBasis of the four input polynomials to QR (EVALUATION), the
 // 2 x 2 tensor product (the plain product loop, :322-334), SetFormat(COEFFICIENT), ScaleAndRound to R, SwitchCRTBasis
 // back to Q.  a0, a1, b0, b1: batches over Q in EVALUATION.  Returns out[0..2] (over Q, COEFFICIENT); 0 on success.
+static int bfv_hps_mult_impl(const ref_polys* a0, const ref_polys* a1, const ref_polys* b0, const ref_polys* b1, ref_ctx* R,
+                             ref_ctx* QR, uint64_t t, ref_polys** out, int outer_threads, double* seconds);
+
 int ref_bfv_hps_mult(const ref_polys* a0, const ref_polys* a1, const ref_polys* b0, const ref_polys* b1, ref_ctx* R,
                      ref_ctx* QR, uint64_t t, ref_polys** out) {
+    return bfv_hps_mult_impl(a0, a1, b0, b1, R, QR, t, out, 1, nullptr);
+}
+// Timed form for the CPU baseline of BASELINE configs[4]: outer_threads > 1 runs an omp-for over the batch (one thread per
+// ciphertext pair, the reference's inner loops serial).  Only the hooked build may do that: in the plain build every
+// NativeVector carries the fork's PimData member, whose bookkeeping is not thread-safe.  *seconds = the multiplication
+// loop only (tables excluded, like the schemes' precomputation).
+int ref_bfv_hps_mult_timed(const ref_polys* a0, const ref_polys* a1, const ref_polys* b0, const ref_polys* b1, ref_ctx* R,
+                           ref_ctx* QR, uint64_t t, ref_polys** out, int outer_threads, double* seconds) {
+#ifndef FHE_HOOKED
+    outer_threads = 1;
+#endif
+    return bfv_hps_mult_impl(a0, a1, b0, b1, R, QR, t, out, outer_threads, seconds);
+}
+
+static int bfv_hps_mult_impl(const ref_polys* a0, const ref_polys* a1, const ref_polys* b0, const ref_polys* b1, ref_ctx* R,
+                             ref_ctx* QR, uint64_t t, ref_polys** out, int outer_threads, double* seconds) {
     int rc = 0;
     std::string err;
-    serial_omp([&] {
+    auto run = [&](auto body) {
+        if (outer_threads > 1) body();
+        else serial_omp(body);
+    };
+    run([&] {
         try {
             ref_ctx* Q = a0->ctx;
             auto mq = moduli_of(Q), mr = moduli_of(R);
@@ -517,8 +540,13 @@ int ref_bfv_hps_mult(const ref_polys* a0, const ref_polys* a1, const ref_polys* 
             std::vector<double> frac;
             std::vector<std::vector<NativeInteger>> modr;
             make_scale_tables(mq, mr, t, frac, modr);
-            for (int k = 0; k < 3; k++) out[k] = new ref_polys{Q, {}};
-            for (size_t i = 0; i < a0->v.size(); i++) {
+            for (int k = 0; k < 3; k++) {
+                out[k] = new ref_polys{Q, {}};
+                out[k]->v.resize(a0->v.size());
+            }
+            auto t0 = std::chrono::steady_clock::now();
+#pragma omp parallel for num_threads(outer_threads) schedule(dynamic) if (outer_threads > 1)
+            for (long i = 0; i < (long)a0->v.size(); i++) {
                 DCRTPoly cv1[2] = {a0->v[i], a1->v[i]}, cv2[2] = {b0->v[i], b1->v[i]};
                 for (auto* cv : {cv1, cv2})
                     for (int k = 0; k < 2; k++)
@@ -536,9 +564,10 @@ int ref_bfv_hps_mult(const ref_polys* a0, const ref_polys* a1, const ref_polys* 
                     cvMult[k] = cvMult[k].ScaleAndRound(R->params, modr, frac, ex.sw.mu);
                     cvMult[k] = cvMult[k].SwitchCRTBasis(Q->params, back.sw.hatInv, back.sw.hatInvPrecon, back.hatModpT,
                                                          back.alphaQModp, back.sw.mu, back.qInv);
-                    out[k]->v.push_back(std::move(cvMult[k]));
+                    out[k]->v[i] = std::move(cvMult[k]);
                 }
             }
+            if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         }
         catch (const std::exception& e) { err = e.what(); rc = 1; }
     });

@@ -1,0 +1,170 @@
+"""BASELINE.json configs[3] and configs[4] at their full batch, sharded over the GPUs of one node.
+
+  cfg3: CKKS ciphertext tensor product (INTT -> pointwise products -> NTT), N = 2^16, 40 towers, 4096 ciphertext pairs
+  cfg4: BFVrns EvalMult, N = 2^15, 16 towers: (a) the primitive pipeline NTT -> tensor product -> INTT and (b) the real
+        RNS core with the HPS technique (ExpandCRTBasis x4, tensor product over QR, INTT, ScaleAndRound, SwitchCRTBasis);
+        batch 4096 pairs; rank 0 also times the reference's own DCRTPoly on the host cores for (b) on a small sample.
+
+One process per GPU (torchrun, like bench.py); the batch is split into contiguous blocks (sharding.plan), no data-path
+collective; NCCL carries the barrier and the max-over-ranks of the device time.  A rank streams its share through
+chunk-sized buffers filled on the device (cfg3's operand set is 172 GB: it cannot be resident on one GPU), so every
+pair is computed, on the values of its chunk slot.
+
+  python tools/config_sweep.py [--gpus N] [--batch 4096] [--chunk 32] [--cpu-sample 8]
+"""
+import argparse
+import ctypes
+import importlib
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def cpu_bfv(n, sq, sr, pairs, t):
+    """The reference's own DCRTPoly running the HPS EvalMult core on all host threads (hooked build, no handle attached)."""
+    from tests import oracle_py
+    so = os.path.join(os.path.dirname(oracle_py.REF_SO), "libopenfhe_hooked.so")
+    if not os.path.exists(so):
+        return None
+    vp, sz, ci, u32, u64 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint32, ctypes.c_uint64
+    H = ctypes.CDLL(so)
+    H.ref_ctx_create.restype = vp; H.ref_ctx_create.argtypes = [u32, u32, vp, vp]
+    H.ref_polys_load.restype = vp; H.ref_polys_load.argtypes = [vp, vp, sz, ci]
+    H.ref_polys_free.argtypes = [vp]
+    H.ref_max_threads.restype = ci
+    H.ref_bfv_hps_mult_timed.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp), ci, ctypes.POINTER(ctypes.c_double)]
+    O = oracle_py.load()
+    p = lambda a: a.ctypes.data_as(vp)
+    q, psi = O.gen_params(60, n, sq + sr)
+    mk = lambda a, b: H.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+    cQ, cR, cQR = mk(0, sq), mk(sq, sq + sr), mk(0, sq + sr)
+    hs = [H.ref_polys_load(cQ, p(O.fill_ring(pairs, n, q[:sq].copy(), 700 + k)), pairs, 0) for k in range(4)]
+    threads = H.ref_max_threads()
+    best = None
+    for _ in range(2):
+        outs, sec = (vp * 3)(), ctypes.c_double()
+        assert H.ref_bfv_hps_mult_timed(hs[0], hs[1], hs[2], hs[3], cR, cQR, t, outs, threads, ctypes.byref(sec)) == 0
+        best = sec.value if best is None else min(best, sec.value)
+        for k in range(3):
+            H.ref_polys_free(outs[k])
+    return {"ciphertext_products_per_s": pairs / best, "seconds": best, "pairs": pairs, "threads": threads,
+            "kind": "reference (its DCRTPoly: ExpandCRTBasis, *, SetFormat, ScaleAndRound, SwitchCRTBasis), omp-for over pairs"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--batch", type=int, default=4096)
+    ap.add_argument("--chunk", type=int, default=32)
+    ap.add_argument("--cpu-sample", type=int, default=8)
+    args = ap.parse_args()
+    world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
+    out_fd = os.dup(1)
+    os.dup2(2, 1)
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            import torch
+            dist.barrier(device_ids=[local])
+            torch.cuda.synchronize()
+
+    def max_ranks(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    pkg = importlib.import_module("upmem--openfhe_b200")
+    sharding = importlib.import_module("upmem--openfhe_b200.sharding")
+    be = pkg.Backend(local, "streams=2,arena_mb=2048")
+    result = {"n_gpus": world, "batch": args.batch, "chunk": args.chunk, "scaling": "strong"}
+
+    def run(name, n, towers_total, make_call, pairs_words):
+        share = sharding.plan(args.batch, 1, world)[rank].batch
+        chunk = min(args.chunk, share)
+        call, cleanup = make_call(chunk)
+        call(chunk)
+        call(chunk)
+        be.sync()
+        barrier()
+        be.timer_start(0)
+        done = 0
+        while done < share:
+            c = min(chunk, share - done)
+            call(c)
+            done += c
+        ms = max_ranks(be.timer_stop(0))
+        cleanup()
+        result[name] = {"ms": ms, "ciphertext_products_per_s": args.batch / (ms * 1e-3), "pairs_per_gpu": share,
+                        "N": n, "towers": towers_total}
+
+    # ---- cfg3
+    n, T = 1 << 16, 40
+    q, psi = pkg.gen_params(60, n, T)
+    ring = pkg.Ring(be, n, q, psi)
+
+    def mk_cfg3(chunk):
+        w = ring.words(chunk) * 8
+        bufs = [be.alloc(w) for _ in range(7)]
+        for i in range(4):
+            ring.fill_uniform(bufs[i], chunk, 900 + i + 17 * rank)
+        return (lambda c: ring.ct_multiply(bufs[4:7], bufs[0:2], bufs[2:4], c, 2)), (lambda: [be.free(b) for b in bufs])
+
+    run("cfg3_ckks_tensor_intt_mul_ntt_n65536_t40", n, T, mk_cfg3, None)
+    ring.close()
+
+    # ---- cfg4
+    n, sq, sr, t = 1 << 15, 16, 17, 65537
+    q, psi = pkg.gen_params(60, n, sq + sr)
+    ring = pkg.Ring(be, n, q, psi)
+    rq = pkg.RingView(ring, 0, sq)
+
+    def mk_cfg4a(chunk):
+        w = rq.words(chunk) * 8
+        bufs = [be.alloc(w) for _ in range(7)]
+        for i in range(4):
+            rq.fill_uniform(bufs[i], chunk, 950 + i + 17 * rank)
+        return (lambda c: rq.ct_multiply(bufs[4:7], bufs[0:2], bufs[2:4], c, 1)), (lambda: [be.free(b) for b in bufs])
+
+    run("cfg4_bfv_primitive_ntt_mul_intt_n32768_t16", n, sq, mk_cfg4a, None)
+    frac, modr = pkg.hps_scale_tables(q[:sq], q[sq:], t)
+    mult = pkg.BfvHpsMult(ring, sq, frac, modr)
+
+    def mk_cfg4b(chunk):
+        w = rq.words(chunk) * 8
+        bufs = [be.alloc(w) for _ in range(7)]
+        for i in range(4):
+            rq.fill_uniform(bufs[i], chunk, 970 + i + 17 * rank)
+        return (lambda c: mult(bufs[4:7], bufs[0:2], bufs[2:4], c)), (lambda: [be.free(b) for b in bufs])
+
+    run("cfg4_bfv_hps_evalmult_core_n32768_q16_r17", n, sq + sr, mk_cfg4b, None)
+    mult.close()
+    rq.close()
+    ring.close()
+    be.close()
+    if rank == 0:
+        if args.cpu_sample > 0:
+            try:
+                result["cfg4_cpu_reference"] = cpu_bfv(n, sq, sr, args.cpu_sample, t)
+            except Exception as ex:                 # noqa: BLE001
+                result["cfg4_cpu_reference"] = {"error": str(ex)[:200]}
+        os.write(out_fd, (json.dumps(result) + "\n").encode())
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
