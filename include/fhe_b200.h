@@ -34,6 +34,9 @@
  *     ScaleAndRound   dcrtpoly-impl.h:1178-1358, 1876-1960        fhe_scale_and_round
  *   DCRTPolyImpl::DropLastElementAndScale / ModReduce            fhe_drop_last_element_and_scale / fhe_mod_reduce
  *     dcrtpoly-impl.h:746-812
+ *   Serial::Serialize / Deserialize (SerType::BINARY) of a       fhe_serialize / fhe_deserialize
+ *     DCRTPoly   utils/serial.h:99-115, dcrtpoly.h:349-365,
+ *     poly.h:322-338, mubintvecnat.h:666-699
  *   FirstPrime / PreviousPrime / RootOfUnity parameter recipe    fhe_gen_params (host side, setup only)
  *     math/nbtheory-impl.h:183-231,334-379;
  *     benchmark/src/poly-benchmark-16k.cpp:82-101
@@ -224,6 +227,30 @@ int fhe_drop_last_element_and_scale(fhe_rescale* plan, fhe_dptr dst, fhe_dptr sr
 /* DCRTPolyImpl::ModReduce (dcrtpoly-impl.h:792-812, BGV modulus switching) with plaintext modulus t > 0;
  * [-t^-1]_{ql} and [t]_{q_i} (bgvrns-cryptoparameters.cpp:91-99) are derived here.  Format is preserved. */
 int fhe_mod_reduce(fhe_rescale* plan, fhe_dptr dst, fhe_dptr src, size_t batch, uint64_t t, int format, int stream);
+
+/* ---- wire format of device-resident polys ---------------------------------------------------- */
+/* The reference's binary serialisation of one DCRTPoly — Serial::Serialize(poly, os, SerType::BINARY)
+ * (utils/serial.h:99-103): a cereal portable-binary stream of DCRTPolyImpl::save (dcrtpoly.h:349-354) over
+ * PolyImpl::save (poly.h:322-327), NativeVectorT::save (mubintvecnat.h:666-675: N raw u64 per tower) and the
+ * params (ildcrtparams.h:350-355, elemparams.h:223-231), BigInteger = bigintdyn (MATHBACKEND 4).  Byte-identical
+ * to what the reference writes for DCRTPoly(params, format) with params = ILDCRTParams(2N, moduli, roots).
+ * fhe_serial_bytes: size of one poly's stream.  fhe_serialize: src [batch][T][N] in HBM -> `batch` consecutive
+ * streams at dst_host (headers written by the host, tower payloads copied from HBM straight into their
+ * places; complete after fhe_sync on `stream`).  fhe_deserialize: parses `batch` consecutive streams (the
+ * reference's own output for any DCRTPoly over native towers, class versions <= 1), checks N, the moduli and
+ * the roots against the ring, and copies the payloads to dst; *format receives the polys' common format,
+ * *consumed the bytes read.  Nothing is written to dst when a stream is rejected (FHE_EINVAL). */
+size_t fhe_serial_bytes(fhe_ring* ring);
+/* Host-only (no device): the stream of one poly with its payload holes left untouched — returns the stream
+ * size, writes the headers when cap suffices, and the byte offset of every tower's N*8 payload to data_off[T]
+ * (psi NULL -> roots written as 0); and the checker fhe_deserialize runs, reporting where the payloads lie. */
+size_t fhe_serial_template(uint32_t N, uint32_t T, const uint64_t* q, const uint64_t* psi, int format, void* blob,
+                           size_t cap, size_t* data_off);
+int fhe_serial_parse(uint32_t N, uint32_t T, const uint64_t* q, const uint64_t* psi, const void* blob, size_t len,
+                     size_t* data_off, int* format, size_t* consumed);
+int fhe_serialize(fhe_ring* ring, void* dst_host, fhe_dptr src, size_t batch, int format, int stream);
+int fhe_deserialize(fhe_ring* ring, fhe_dptr dst, const void* src_host, size_t len, size_t batch, int* format,
+                    size_t* consumed, int stream);
 
 /* seeded uniform coefficients in [0, q_tower) (synthetic inputs for tests and benchmarks) */
 int fhe_fill_uniform(fhe_ring* ring, fhe_dptr dst, size_t batch, uint64_t seed, int stream);

@@ -23,6 +23,7 @@
 #include <cstdint>
 #include <memory>
 #include <stdexcept>
+#include <ostream>
 #include <string>
 #include <vector>
 
@@ -182,6 +183,27 @@ public:
     PimManager::check(fhe_sync(ctx(), stream_), "PimDCRTPoly::sync");
   }
   std::vector<uint64_t> GetValues() const { std::vector<uint64_t> v(words()); sync(v.data()); return v; }
+
+  /* Wire format: `batch` consecutive streams, each what Serial::Serialize(poly, os, SerType::BINARY) writes for the
+   * DCRTPoly it stands for (utils/serial.h:99-103, dcrtpoly.h:349-354).  Blocking. */
+  std::string Serialize() const {
+    std::string blob(fhe_serial_bytes(ring_->handle()) * batch_, '\0');
+    PimManager::check(fhe_serialize(ring_->handle(), &blob[0], d_, batch_, (int)format_, stream_), "Serialize");
+    PimManager::check(fhe_sync(ctx(), stream_), "Serialize");
+    return blob;
+  }
+  void Serialize(std::ostream &os) const { std::string b = Serialize(); os.write(b.data(), (std::streamsize)b.size()); }
+  /* Serial::Deserialize (utils/serial.h:111-115) of `batch` consecutive streams into a device-resident batch; throws
+   * when a stream is malformed or was written for another ring.  *consumed = bytes read. */
+  static PimDCRTPoly Deserialize(std::shared_ptr<PimRing> ring, const void *blob, size_t len, size_t batch,
+                                 size_t *consumed = nullptr, int stream = 0) {
+    PimDCRTPoly p(std::move(ring), batch, PIM_EVALUATION, nullptr, stream);
+    int fmt = 0;
+    PimManager::check(fhe_deserialize(p.ring_->handle(), p.d_, blob, len, batch, &fmt, consumed, stream), "Deserialize");
+    PimManager::check(fhe_sync(p.ctx(), stream), "Deserialize");
+    p.format_ = fmt == 0 ? PIM_EVALUATION : PIM_COEFFICIENT;
+    return p;
+  }
 
   PimDCRTPoly Plus(const PimDCRTPoly &rhs) const { check(rhs, "add", false); return binary(rhs, FHE_OP_ADD); }
   PimDCRTPoly Minus(const PimDCRTPoly &rhs) const { check(rhs, "subtract", false); return binary(rhs, FHE_OP_SUB); }

@@ -10,6 +10,7 @@
 #include "math/math-hal.h"
 #include "math/nbtheory.h"
 #include "utils/parallel.h"
+#include "utils/serial.h"
 
 #include <chrono>
 #include <cstdint>
@@ -597,6 +598,66 @@ int ref_vec_modop(int kind, uint64_t* data, size_t n, uint64_t mod, uint64_t p, 
     }
     catch (...) {
         return 1;
+    }
+}
+
+// The reference's own binary wire format of one DCRTPoly (Serial::Serialize(..., SerType::BINARY), utils/serial.h:99-103:
+// a cereal PortableBinaryOutputArchive over DCRTPolyImpl::save, dcrtpoly.h:349-354).  Returns the byte count; copies
+// min(count, cap) bytes to out.
+size_t ref_polys_serialize(const ref_polys* p, size_t index, uint8_t* out, size_t cap) {
+    try {
+        std::stringstream ss;
+        Serial::Serialize(p->v.at(index), ss, SerType::BINARY);
+        std::string s = ss.str();
+        if (out && cap) std::memcpy(out, s.data(), std::min(cap, s.size()));
+        return s.size();
+    }
+    catch (const std::exception& e) {
+        g_ref_err = e.what();
+        return 0;
+    }
+}
+// Same poly, but every tower owns a private copy of its params, so the stream carries the tower params of
+// ILDCRTParams inline instead of by id (a shape the reference's reader accepts and other producers may write).
+size_t ref_polys_serialize_detached(const ref_polys* p, size_t index, uint8_t* out, size_t cap) {
+    try {
+        DCRTPoly poly(p->v.at(index));
+        for (uint32_t t = 0; t < p->ctx->T; t++) {
+            const NativePoly& src = poly.GetElementAtIndex(t);
+            auto own = std::make_shared<ILNativeParams>(*src.GetParams());
+            NativePoly np(own, src.GetFormat(), false);
+            np.SetValues(src.GetValues(), src.GetFormat());
+            poly.SetElementAtIndex(t, std::move(np));
+        }
+        std::stringstream ss;
+        Serial::Serialize(poly, ss, SerType::BINARY);
+        std::string s = ss.str();
+        if (out && cap) std::memcpy(out, s.data(), std::min(cap, s.size()));
+        return s.size();
+    }
+    catch (const std::exception& e) {
+        g_ref_err = e.what();
+        return 0;
+    }
+}
+// Serial::Deserialize of one DCRTPoly (utils/serial.h:111-115).  The handle keeps ctx c for (N, T) only: the poly carries
+// the params it was serialised with.  NULL if the reference threw or the shape differs from c.
+ref_polys* ref_polys_deserialize(ref_ctx* c, const uint8_t* bytes, size_t len) {
+    try {
+        std::stringstream ss(std::string(reinterpret_cast<const char*>(bytes), len));
+        DCRTPoly poly;
+        Serial::Deserialize(poly, ss, SerType::BINARY);
+        if (poly.GetNumOfElements() != c->T || poly.GetRingDimension() != c->N) {
+            g_ref_err = "deserialised shape differs from the context";
+            return nullptr;
+        }
+        auto* p = new ref_polys{c, {}};
+        p->v.push_back(std::move(poly));
+        return p;
+    }
+    catch (const std::exception& e) {
+        g_ref_err = e.what();
+        return nullptr;
     }
 }
 

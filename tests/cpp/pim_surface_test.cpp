@@ -162,6 +162,15 @@ static void test_dcrtpoly_ext(uint32_t N, uint32_t sq, uint32_t sp, size_t B) {
     try { y.AutomorphismTransform(6); } catch (const pim_math_error&) { threw = true; }
     EXPECT(threw, "even automorphism index must throw");
 
+    // wire format round trip (bytes against the reference are pinned in tests/test_gpu_serial.py)
+    std::string blob = y.Serialize();
+    size_t used = 0;
+    PimDCRTPoly back = PimDCRTPoly::Deserialize(ring, blob.data(), blob.size(), B, &used);
+    EXPECT(used == blob.size() && back.GetFormat() == PIM_EVALUATION && back.GetValues() == hy, "Serialize/Deserialize N=%u", N);
+    threw = false;
+    try { PimDCRTPoly::Deserialize(ringQ, blob.data(), blob.size(), B); } catch (const std::exception&) { threw = true; }
+    EXPECT(threw, "a stream written for another ring must be rejected");
+
     PimBasis qToP(ringQ, ringP), pToQ(ringP, ringQ);
     orc_approx_mod_up(oQ, oP, exp.data(), hx.data(), B, 0);
     PimDCRTPoly up = x.ApproxModUp(qToP, ring);

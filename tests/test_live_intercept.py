@@ -43,6 +43,10 @@ def hooked():
     H.ref_polys_approx_switch.argtypes = [vp, vp]
     H.ref_polys_approx_mod_down.restype = vp
     H.ref_polys_approx_mod_down.argtypes = [vp, vp, vp, u64]
+    H.ref_polys_serialize.restype = sz
+    H.ref_polys_serialize.argtypes = [vp, sz, vp, sz]
+    H.ref_polys_deserialize.restype = vp
+    H.ref_polys_deserialize.argtypes = [vp, vp, sz]
     return H
 
 
@@ -249,3 +253,40 @@ def test_resident_neighbouring_methods(hooked, oracle, pkg):
         H.ref_polys_free(h)
     for c in (cQ, cP, cQP, cRest):
         H.ref_ctx_destroy(c)
+
+
+@pytest.mark.gpu
+def test_resident_poly_serialises_through_the_reference(hooked, oracle, pkg):
+    """Serial::Serialize of the reference (DCRTPolyImpl::save, dcrtpoly.h:349-354) reads the towers through the const
+    accessor, so a device-resident result is downloaded once and written in the wire format; the stream equals the one
+    fhe_serialize writes for the same values, and the reference's Deserialize gives a poly the hook can use again."""
+    H = hooked
+    n, towers = 1 << 11, 3
+    q, psi = oracle.gen_params(60, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    a, b = oracle.fill_ring(1, n, q, 51), oracle.fill_ring(1, n, q, 52)
+    ctx = H.ref_ctx_create(n, towers, p(q), p(psi))
+    ha, hb = H.ref_polys_load(ctx, p(a), 1, 0), H.ref_polys_load(ctx, p(b), 1, 0)
+    assert H.ref_polys_set_pim(ha, 1) == 0, H.ref_last_error()
+    assert H.ref_polys_op(ha, hb, 2, 1) >= 0                            # a *= b on the device
+    _, down0 = counters(H)
+    size = H.ref_polys_serialize(ha, 0, None, 0)
+    blob = np.zeros(size, np.uint8)
+    assert H.ref_polys_serialize(ha, 0, p(blob), size) == size
+    assert counters(H)[1] - down0 == 1                                  # one download, the second call found the host copy current
+    want = octx.elementwise(2, a, b)
+    be = pkg.Backend(0)
+    ring = pkg.Ring(be, n, q, psi)
+    mine = pkg.DCRTPolyBatch(ring, 1, pkg.EVALUATION, want).Serialize()
+    assert mine.tobytes() == blob.tobytes()
+    hc = H.ref_polys_deserialize(ctx, p(blob), size)
+    assert hc, H.ref_last_error()
+    assert H.ref_polys_set_pim(hc, 1) == 0, H.ref_last_error()
+    assert H.ref_polys_op(hc, hb, 0, 1) >= 0                            # the loaded poly goes back through the hook
+    res = np.empty_like(a)
+    H.ref_polys_store(hc, p(res))
+    assert np.array_equal(res, octx.elementwise(0, want, b))
+    ring.close(); be.close()
+    for h in (ha, hb, hc):
+        H.ref_polys_free(h)
+    H.ref_ctx_destroy(ctx)

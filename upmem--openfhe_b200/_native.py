@@ -71,6 +71,11 @@ SIGNATURES = {
     "fhe_rescale_tables": (ci, [vp, vp, vp]),
     "fhe_drop_last_element_and_scale": (ci, [vp, u64, u64, sz, ci, ci]),
     "fhe_mod_reduce": (ci, [vp, u64, u64, sz, u64, ci, ci]),
+    "fhe_serial_bytes": (sz, [vp]),
+    "fhe_serial_template": (sz, [u32, u32, vp, vp, ci, vp, sz, vp]),
+    "fhe_serial_parse": (ci, [u32, u32, vp, vp, vp, sz, vp, ctypes.POINTER(ci), ctypes.POINTER(sz)]),
+    "fhe_serialize": (ci, [vp, vp, u64, sz, ci, ci]),
+    "fhe_deserialize": (ci, [vp, u64, vp, sz, sz, ctypes.POINTER(ci), ctypes.POINTER(sz), ci]),
     "fhe_fill_uniform": (ci, [vp, u64, sz, u64, ci]),
     "fhe_vec_op": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),
     "fhe_vec_op_scalar": (ci, [vp, ci, u64, u64, u64, sz, u64, ci]),

@@ -8,6 +8,7 @@
 #include "hostmath.h"
 #include "kernels.h"
 #include "modarith.cuh"
+#include "serial.h"
 
 #include <algorithm>
 #include <cstdarg>
@@ -15,6 +16,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -153,6 +155,8 @@ struct fhe_ring {
     void* d_twF = nullptr;
     void* d_twI = nullptr;
     void* d_invc = nullptr;
+    std::mutex layout_mu;      // wire-format layout of one poly over this ring, built on first use (serial.h)
+    std::unique_ptr<serial::Layout> layout;
 };
 
 static int get_stream(fhe_ctx* ctx, int stream, cudaStream_t* out) {
@@ -1396,6 +1400,110 @@ extern "C" int fhe_ntt_host(fhe_ring* r, uint64_t* x, size_t batch, int inverse)
         CUDA_TRY(cudaMemcpyAsync(x + b0 * hp.item_words, d, words * 8, cudaMemcpyDeviceToHost, s));
     }
     for (size_t i = 0; i < hp.nslots; i++) CUDA_TRY(cudaStreamSynchronize(r->ctx->streams[i]));
+    return FHE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// wire format: Serial::Serialize / Deserialize (SerType::BINARY) of device-resident polys (serial.h)
+// ---------------------------------------------------------------------------------------------
+static const serial::Layout& ring_layout(fhe_ring* r) {
+    std::lock_guard<std::mutex> g(r->layout_mu);
+    if (!r->layout) r->layout.reset(new serial::Layout(serial::make_layout(r->dev.N, r->q, r->psi)));
+    return *r->layout;
+}
+
+// towers 1.. of the canonical stream are equally spaced, so one byte-granular 2-D copy moves them all
+static cudaError_t copy_payload(uint8_t* blob, const std::vector<size_t>& off, uint64_t* dev, uint32_t T, uint32_t N, bool to_host,
+                                cudaStream_t s) {
+    const size_t row = (size_t)N * 8;
+    auto one = [&](uint32_t t) {
+        return to_host ? cudaMemcpyAsync(blob + off[t], dev + (size_t)t * N, row, cudaMemcpyDeviceToHost, s)
+                       : cudaMemcpyAsync(dev + (size_t)t * N, blob + off[t], row, cudaMemcpyHostToDevice, s);
+    };
+    cudaError_t e = one(0);
+    if (e != cudaSuccess || T == 1) return e;
+    bool even = true;
+    for (uint32_t t = 2; t < T; t++) even = even && (off[t] - off[t - 1] == off[2] - off[1]);
+    if (T == 2 || !even) {
+        for (uint32_t t = 1; t < T && e == cudaSuccess; t++) e = one(t);
+        return e;
+    }
+    const size_t pitch = off[2] - off[1];
+    return to_host ? cudaMemcpy2DAsync(blob + off[1], pitch, dev + N, row, row, T - 1, cudaMemcpyDeviceToHost, s)
+                   : cudaMemcpy2DAsync(dev + N, row, blob + off[1], pitch, row, T - 1, cudaMemcpyHostToDevice, s);
+}
+
+// host-only views of the format (no device needed): the header bytes around the payload holes, and the checker
+extern "C" size_t fhe_serial_template(uint32_t N, uint32_t T, const uint64_t* q, const uint64_t* psi, int format, void* blob,
+                                      size_t cap, size_t* data_off) {
+    if (!q || T == 0 || N == 0 || (format != 0 && format != 1)) { fail(FHE_EINVAL, "fhe_serial_template: bad argument"); return 0; }
+    std::vector<uint64_t> vq(q, q + T), vpsi;
+    if (psi) vpsi.assign(psi, psi + T);
+    serial::Layout L = serial::make_layout(N, vq, vpsi);
+    if (data_off) std::copy(L.data_off.begin(), L.data_off.end(), data_off);
+    if (blob && cap >= L.bytes) serial::write_headers(L, (uint8_t*)blob, (uint32_t)format);
+    return L.bytes;
+}
+extern "C" int fhe_serial_parse(uint32_t N, uint32_t T, const uint64_t* q, const uint64_t* psi, const void* blob, size_t len,
+                                size_t* data_off, int* format, size_t* consumed) {
+    if (!q || !blob || T == 0) return fail(FHE_EINVAL, "fhe_serial_parse: bad argument");
+    std::vector<uint64_t> vq(q, q + T), vpsi;
+    if (psi) vpsi.assign(psi, psi + T);
+    serial::Parsed ps;
+    std::string err;
+    if (!serial::parse((const uint8_t*)blob, len, N, vq, vpsi, ps, err)) return fail(FHE_EINVAL, "fhe_serial_parse: %s", err.c_str());
+    if (data_off) std::copy(ps.data_off.begin(), ps.data_off.end(), data_off);
+    if (format) *format = (int)ps.format;
+    if (consumed) *consumed = ps.consumed;
+    return FHE_OK;
+}
+
+extern "C" size_t fhe_serial_bytes(fhe_ring* r) { return r ? ring_layout(r).bytes : 0; }
+
+extern "C" int fhe_serialize(fhe_ring* r, void* dst_host, fhe_dptr src, size_t batch, int format, int stream) {
+    cudaStream_t s;
+    int rc = ring_stream(r, stream, &s);
+    if (rc) return rc;
+    if (format != 0 && format != 1) return fail(FHE_EINVAL, "fhe_serialize: format must be 0 or 1");
+    if (batch == 0) return FHE_OK;
+    if (!dst_host || !src) return fail(FHE_EINVAL, "fhe_serialize: null pointer");
+    const serial::Layout& L = ring_layout(r);
+    const uint32_t N = r->dev.N, T = r->dev.T;
+    uint8_t* out = (uint8_t*)dst_host;
+    uint64_t* dev = (uint64_t*)(uintptr_t)src;
+    for (size_t b = 0; b < batch; b++) {
+        serial::write_headers(L, out + b * L.bytes, (uint32_t)format);
+        CUDA_TRY(copy_payload(out + b * L.bytes, L.data_off, dev + b * (size_t)T * N, T, N, true, s));
+    }
+    return FHE_OK;
+}
+
+extern "C" int fhe_deserialize(fhe_ring* r, fhe_dptr dst, const void* src_host, size_t len, size_t batch, int* format,
+                               size_t* consumed, int stream) {
+    cudaStream_t s;
+    int rc = ring_stream(r, stream, &s);
+    if (rc) return rc;
+    if (consumed) *consumed = 0;
+    if (batch == 0) return FHE_OK;
+    if (!dst || !src_host) return fail(FHE_EINVAL, "fhe_deserialize: null pointer");
+    const uint32_t N = r->dev.N, T = r->dev.T;
+    const uint8_t* in = (const uint8_t*)src_host;
+    uint64_t* dev = (uint64_t*)(uintptr_t)dst;
+    // every stream is checked before the first byte moves, so a bad batch leaves dst untouched
+    std::vector<serial::Parsed> ps(batch);
+    size_t pos = 0;
+    for (size_t b = 0; b < batch; b++) {
+        std::string err;
+        if (!serial::parse(in + pos, len - pos, N, r->q, r->psi, ps[b], err))
+            return fail(FHE_EINVAL, "fhe_deserialize: poly %zu: %s", b, err.c_str());
+        if (ps[b].format != ps[0].format) return fail(FHE_EINVAL, "fhe_deserialize: poly %zu: format differs from poly 0's", b);
+        for (auto& o : ps[b].data_off) o += pos;
+        pos += ps[b].consumed;
+    }
+    for (size_t b = 0; b < batch; b++)
+        CUDA_TRY(copy_payload(const_cast<uint8_t*>(in), ps[b].data_off, dev + b * (size_t)T * N, T, N, false, s));
+    if (format) *format = (int)ps[0].format;
+    if (consumed) *consumed = pos;
     return FHE_OK;
 }
 

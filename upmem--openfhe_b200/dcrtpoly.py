@@ -184,6 +184,28 @@ class Ring:
     def ntt_host(self, x, batch, inverse=False):
         N.check(N.lib.fhe_ntt_host(self.h, _ptr(x), batch, 1 if inverse else 0))
 
+    # wire format (utils/serial.h:99-115, SerType::BINARY)
+    def serial_bytes(self):
+        """Bytes of one serialised DCRTPoly over this ring."""
+        return int(N.lib.fhe_serial_bytes(self.h))
+
+    def serialize(self, src, batch, fmt, stream=0):
+        """`batch` device-resident polys -> `batch` consecutive streams, each what the reference's
+        Serial::Serialize(poly, os, SerType::BINARY) writes (dcrtpoly.h:349-354)."""
+        out = np.empty(self.serial_bytes() * batch, np.uint8)
+        N.check(N.lib.fhe_serialize(self.h, _ptr(out), src, batch, fmt, stream))
+        self.be.sync(stream)
+        return out
+
+    def deserialize(self, dst, blob, batch, stream=0):
+        """Serial::Deserialize of `batch` consecutive streams into HBM; returns (format, bytes consumed).
+        Raises if a stream does not belong to this ring (N, moduli, roots) or is malformed."""
+        blob = np.frombuffer(blob, np.uint8) if not isinstance(blob, np.ndarray) else np.ascontiguousarray(blob, np.uint8)
+        fmt, used = ctypes.c_int(), ctypes.c_size_t()
+        N.check(N.lib.fhe_deserialize(self.h, dst, _ptr(blob), blob.size, batch, ctypes.byref(fmt), ctypes.byref(used), stream))
+        self.be.sync(stream)
+        return fmt.value, used.value
+
 
 class DCRTPolyBatch:
     """`batch` DCRTPolys resident in HBM; operators mirror DCRTPolyImpl."""
@@ -209,6 +231,17 @@ class DCRTPolyBatch:
     def to_host(self):
         out = self.ring.be.d2h(self.dptr, self.nwords, self.stream)
         return out.reshape(self.batch, self.ring.towers, self.ring.n)
+
+    def Serialize(self):
+        """The batch as consecutive binary streams of the reference's wire format (one per poly)."""
+        return self.ring.serialize(self.dptr, self.batch, self.format, self.stream)
+
+    @classmethod
+    def Deserialize(cls, ring, blob, batch, stream=0):
+        """A device-resident batch from `batch` consecutive streams (the format comes from the streams)."""
+        p = cls(ring, batch, stream=stream)
+        p.format, _ = ring.deserialize(p.dptr, blob, batch, stream)
+        return p
 
     def clone(self):
         c = DCRTPolyBatch(self.ring, self.batch, self.format, stream=self.stream)
