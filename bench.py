@@ -292,6 +292,36 @@ def main():
                             "h2d_bytes_per_step": 2 * words * 8, "d2h_bytes_per_step": 2 * words * 8,
                             "api": "fhe_dcrt_multi_op_host(ADD, MUL): a + b and a * b both returned"}}
 
+    # ---- optional result gather (north_star: "NCCL over NVLink only to gather results"): every rank receives every
+    # rank's product of one step, HBM to HBM; device-timed on torch's stream, max over ranks ----
+    gather = None
+    if dist is not None:
+        import torch
+        step()
+        be.sync()
+        dev = torch.device("cuda", local)
+        g = sharding.gather_device(dd, words, dist, dev)             # warm-up: NCCL channels, output allocation
+        torch.cuda.synchronize()
+        own = g[rank, :4096].cpu().numpy().view("uint64")
+        assert (own == be.d2h(dd, 4096)).all(), "gathered block differs from this rank's result"
+        del g
+        reps_g = 5
+        barrier(dist, local)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for _ in range(reps_g):
+            g = sharding.gather_device(dd, words, dist, dev)
+        ev1.record()
+        torch.cuda.synchronize()
+        g_ms = max_over_ranks(dist, local, ev0.elapsed_time(ev1) / reps_g)
+        del g
+        step_ms = ms / args.steps
+        gather = {"what": "all_gather_into_tensor of each rank's modmul result of one step (NCCL over NVLink/NVSwitch)",
+                  "bytes_per_rank": words * 8, "ms": g_ms, "recv_gbs_per_rank": (world - 1) * words * 8 / (g_ms * 1e-3) / 1e9,
+                  "value_with_gather": world * 2 * coeffs / ((step_ms + g_ms) * 1e-3),
+                  "note": "value (without the gather) is the headline; a step moves 1.6 GB through HBM in "
+                          f"{step_ms:.3f} ms, its 268 MB product takes {g_ms:.2f} ms to reach the other {world - 1} GPU(s)"}
+
     sampler.stop_flag = True
     sampler.join()
 
@@ -324,7 +354,7 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "N": N_RING, "towers": TOWERS, "batch_per_gpu": BATCH,
                        "l2": "operands 268 MB each > 126 MB L2: no flush needed", "parallelism": f"batch-sharded x{world}"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "gather": gather,
             "clocks": sampler.summary(), "extra": extra,
         }
         emit(line)

@@ -106,3 +106,21 @@ def gather_results(local, shards, n, dist, device=None):
         if s.units:
             full[s.b0:s.b1, s.t0:s.t1, :] = host[s.rank, :s.units * n].reshape(s.batch, s.towers, n)
     return full
+
+
+class _DeviceWords:
+    """A device buffer of the C ABI (plain address) seen by torch through the CUDA array interface, as int64."""
+
+    def __init__(self, dptr, nwords):
+        self.__cuda_array_interface__ = {"shape": (int(nwords),), "typestr": "<i8", "data": (int(dptr), False), "version": 2}
+
+
+def gather_device(dptr, nwords, dist, device):
+    """all-gather every rank's `nwords` result words, HBM to HBM over NCCL (NVLink / NVSwitch), without a host copy:
+    returns an int64 torch tensor [world][nwords] on `device`.  The caller synchronises its own stream first —
+    torch enqueues the collective behind ITS current stream, not the C ABI's."""
+    import torch
+    src = torch.as_tensor(_DeviceWords(dptr, nwords), device=device)
+    out = torch.empty(dist.get_world_size() * int(nwords), dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(out, src)
+    return out.view(dist.get_world_size(), int(nwords))
