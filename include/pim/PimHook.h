@@ -19,7 +19,9 @@
 
 #include "PimDCRTPoly.h"
 
+#include <atomic>
 #include <cstring>
+#include <cstdlib>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -151,7 +153,13 @@ inline Staging &staging() { static Staging s; return s; }
 /* makes `towers` resident (uploading them if they are not yet) and returns the device copy */
 template <class Towers>
 inline std::shared_ptr<Resident> ensure_device(PimManager *pim, const Towers &towers, std::shared_ptr<Resident> &res) {
-  if (res && res->towers == towers.size() && res->n == towers[0].GetRingDimension()) return res;
+  auto cur = std::atomic_load(&res);
+  if (cur && cur->towers == towers.size() && cur->n == towers[0].GetRingDimension()) return cur;
+  /* first use of this operand: several threads may share it (a key polynomial inside an OpenMP loop), one uploads */
+  static std::mutex create_mu;
+  std::lock_guard<std::mutex> create(create_mu);
+  cur = std::atomic_load(&res);
+  if (cur && cur->towers == towers.size() && cur->n == towers[0].GetRingDimension()) return cur;
   auto r = std::make_shared<Resident>();
   r->ring = ring_of(pim, towers);
   r->ctx = pim->context();
@@ -168,7 +176,7 @@ inline std::shared_ptr<Resident> ensure_device(PimManager *pim, const Towers &to
     PimManager::check(fhe_sync(r->ctx, 0), "pim hook: sync");   /* the staging block is reused after this */
   }
   resident_uploads()++;
-  res = r;
+  std::atomic_store(&res, r);
   return r;
 }
 
@@ -186,12 +194,72 @@ inline void sync_host(Towers &towers, const std::shared_ptr<Resident> &res, Form
     PimManager::check(fhe_d2h(res->ctx, h, res->d, res->towers * bytes, 0), "pim hook: download");
     PimManager::check(fhe_sync(res->ctx, 0), "pim hook: sync");
     for (size_t t = 0; t < res->towers; t++) {       /* in place: same length and modulus */
+      if (towers[t].IsEmpty()) towers[t].SetValuesToZero();     /* a device result: host storage appears on first read */
       memcpy(const_cast<uint64_t *>(words(towers[t].GetValues())), h + t * res->n, bytes);
       towers[t].OverrideFormat(format);               /* poly.h:179-181: sets the format without transforming */
     }
   }
   resident_downloads()++;
   res->device_newer = false;
+}
+
+/* FHE_B200_HOOK_SYNC=1: every hooked operator waits for its kernels (per-operation latency instead of the default
+ * enqueue-and-return, where only a host read waits) — for measurements */
+inline void finish(fhe_ctx *ctx) {
+  static const bool on = [] { const char *e = std::getenv("FHE_B200_HOOK_SYNC"); return e && *e && *e != '0'; }();
+  if (on) PimManager::check(fhe_sync(ctx, 0), "pim hook: sync");
+}
+
+/* a second device copy of the same values (copy construction / assignment of a resident DCRTPoly): HBM to HBM, so a
+ * copy of a device result costs no download and a copy of an uploaded operand no second upload */
+inline std::shared_ptr<Resident> clone_resident(const std::shared_ptr<Resident> &src) {
+  if (!src) return nullptr;
+  auto r = std::make_shared<Resident>();
+  std::lock_guard<std::mutex> lock(src->mu);
+  r->ring = src->ring;
+  r->ctx = src->ctx;
+  r->towers = src->towers;
+  r->n = src->n;
+  const size_t bytes = r->towers * r->n * sizeof(uint64_t);
+  PimManager::check(fhe_alloc(r->ctx, bytes, &r->d), "pim hook: device buffer");
+  PimManager::check(fhe_d2d(r->ctx, r->d, src->d, bytes, 0), "pim hook: device copy");
+  r->device_newer = src->device_newer;
+  return r;
+}
+
+/* dst = src for an attached DCRTPoly: src is uploaded on its first copy (and stays resident, so later copies and
+ * operators find it in HBM), dst becomes a device-only poly — towers without host storage plus an HBM-to-HBM copy.
+ * Returns false when there is nothing to upload (empty towers): the caller copies on the host as the reference does. */
+template <class Towers>
+inline bool copy_resident(PimManager *pim, Towers &dst, std::shared_ptr<Resident> &rdst, const Towers &src,
+                          std::shared_ptr<Resident> &rsrc) {
+  if (!pim || src.empty()) return false;
+  auto from = std::atomic_load(&rsrc);
+  if (!from) {
+    for (const auto &t : src)
+      if (t.IsEmpty()) return false;
+    from = ensure_device(pim, src, rsrc);
+  }
+  auto c = clone_resident(from);
+  c->device_newer = true;
+  Towers shell;
+  shell.reserve(src.size());
+  for (const auto &t : src) shell.emplace_back(t.GetParams(), t.GetFormat(), false);
+  dst = std::move(shell);
+  rdst = c;
+  return true;
+}
+
+/* Process-wide opt-in: with FHE_B200_ATTACH=1 in the environment every DCRTPoly is born with the backend handle
+ * attached (the fork attaches it per object with SetPim, dcrtpoly.h:410-412), so unmodified callers — the reference's
+ * own benchmark/src/poly-benchmark-16k.cpp — run their +, *, SwitchFormat on the device. */
+inline std::shared_ptr<PimManager> default_handle() {
+  static std::shared_ptr<PimManager> h = [] {
+    const char *e = std::getenv("FHE_B200_ATTACH");
+    if (!e || !*e || *e == '0') return std::shared_ptr<PimManager>();
+    return std::shared_ptr<PimManager>(PimManager::getPim(4), [](PimManager *) {});
+  }();
+  return h;
 }
 
 /* a (op)= b on the device copies; nothing crosses PCIe when both are already resident */
@@ -202,6 +270,7 @@ inline bool resident_eq(PimManager *pim, const Towers &a, std::shared_ptr<Reside
   auto da = ensure_device(pim, a, ra);
   auto db = (&a == &b) ? da : ensure_device(pim, b, rb);
   PimManager::check(fhe_dcrt_op(da->ring->handle(), op, da->d, da->d, db->d, 1, 0), "pim hook: dcrt op");
+  finish(da->ctx);
   std::lock_guard<std::mutex> lock(da->mu);
   da->device_newer = true;
   return true;
@@ -222,6 +291,7 @@ inline bool resident_binary(PimManager *pim, const Towers &a, std::shared_ptr<Re
   r->n = da->n;
   PimManager::check(fhe_alloc(r->ctx, r->towers * r->n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
   PimManager::check(fhe_dcrt_op(da->ring->handle(), op, r->d, da->d, db->d, 1, 0), "pim hook: dcrt op");
+  finish(da->ctx);
   r->device_newer = true;
   rout = r;
   return true;
@@ -233,6 +303,7 @@ inline bool resident_switch_format(PimManager *pim, const Towers &a, std::shared
   auto da = ensure_device(pim, a, ra);
   PimManager::check(to_evaluation ? fhe_ntt_forward(da->ring->handle(), da->d, 1, 0) : fhe_ntt_inverse(da->ring->handle(), da->d, 1, 0),
                     "pim hook: transform");
+  finish(da->ctx);
   std::lock_guard<std::mutex> lock(da->mu);
   da->device_newer = true;
   return true;
@@ -296,6 +367,7 @@ inline bool resident_automorphism(PimManager *pim, const Towers &a, std::shared_
   auto da = ensure_device(pim, a, ra);
   auto r = new_resident(pim, out);
   PimManager::check(fhe_automorphism(da->ring->handle(), r->d, da->d, 1, k, format, 0), "pim hook: automorphism");
+  finish(da->ctx);
   rout = r;
   return true;
 }
@@ -363,6 +435,51 @@ inline bool resident_mod_down(PimManager *pim, const Towers &a, std::shared_ptr<
     PimManager::check(fhe_approx_mod_down(plan.plan->handle(), r->d, da->d, 1, t, 0), "pim hook: mod down");
   }
   rout = r;
+  return true;
+}
+
+/* DCRTPolyImpl::ApproxModUp (dcrtpoly-impl.h:1085-1133): a over Q (either format) -> out over QP, EVALUATION.
+ * `out` = host shells of the QP towers (moduli and roots only). */
+template <class Towers>
+inline bool resident_mod_up(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
+                            std::shared_ptr<Resident> &rout, int format) {
+  if (!pim || a.empty() || out.size() <= a.size()) return false;
+  auto da = ensure_device(pim, a, ra);
+  auto r = new_resident(pim, out);
+  const size_t sq = a.size(), sp = out.size() - sq;
+  static std::mutex mu;
+  static std::map<std::pair<PimRing *, size_t>, std::shared_ptr<PimRing>> views;      /* the P towers of a QP ring */
+  std::shared_ptr<PimRing> rp;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto key = std::make_pair(r->ring.get(), sq);
+    auto it = views.find(key);
+    if (it == views.end()) it = views.emplace(key, PimRing::View(r->ring, (uint32_t)sq, (uint32_t)sp)).first;
+    rp = it->second;
+  }
+  auto plan = basis_for(da->ring, rp);
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_approx_mod_up(plan.plan->handle(), r->d, da->d, 1, format, 0), "pim hook: mod up");
+  }
+  finish(r->ctx);
+  rout = r;
+  return true;
+}
+
+/* DCRTPolyImpl::ModReduce (dcrtpoly-impl.h:792-812, BGV modulus switching): like resident_rescale with the plaintext
+ * modulus t; the format is preserved */
+template <class Towers>
+inline bool resident_mod_reduce(PimManager *pim, const std::shared_ptr<Resident> &full, const Towers &rest,
+                                std::shared_ptr<Resident> &res, uint64_t t, int format) {
+  auto plan = rescale_for(full->ring);
+  auto r = new_resident(pim, rest);
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_mod_reduce(plan.plan->handle(), r->d, full->d, 1, t, format, 0), "pim hook: mod reduce");
+  }
+  finish(r->ctx);
+  res = r;
   return true;
 }
 

@@ -53,7 +53,7 @@ ACCESSORS = """
     /* B200 intercept, resident form (pim/PimHook.h): host view of the towers.  const: refresh from the device copy
      * if that is newer.  non-const: refresh, then drop the device copy (the caller may write). */
     const std::vector<PolyType>& PimHostVectors() const {
-        if (pimres_) pimhook::sync_host(m_vectors_, pimres_, m_format);
+        if (auto r = std::atomic_load(&pimres_)) pimhook::sync_host(m_vectors_, r, m_format);
         return m_vectors_;
     }
     std::vector<PolyType>& PimHostVectors() {
@@ -63,6 +63,17 @@ ACCESSORS = """
         }
         return m_vectors_;
     }
+    /* copy construction / assignment: an attached source is copied HBM to HBM (uploaded first if it never was) */
+    void PimCopyFrom(const DCRTPolyImpl& e) {
+        if (&e == this) return;
+        std::shared_ptr<pimhook::Resident> r;
+        if (e.pim && pimhook::copy_resident(e.pim.get(), m_vectors_, r, e.m_vectors_, e.pimres_)) {
+            pimres_ = r;
+            return;
+        }
+        m_vectors_ = e.PimHostVectors();
+        pimres_.reset();
+    }
     mutable std::vector<PolyType> m_vectors_;
     mutable std::shared_ptr<pimhook::Resident> pimres_;
 """
@@ -71,7 +82,7 @@ HOOK_EQ = ("\n    if (pim && pimhook::resident_eq(pim.get(), m_vectors_, pimres_
 
 
 HOOK_BIN = ("        if (pim) {\n"
-            "            DCRTPolyType dev(m_params, m_format, true);\n"
+            "            DCRTPolyType dev(m_params, m_format, false);\n"
             "            if (pimhook::resident_binary(pim.get(), m_vectors_, pimres_, rhs.m_vectors_, rhs.pimres_, dev.m_vectors_,\n"
             "                                         dev.pimres_, %s)) {\n"
             "                dev.pim = pim;\n"
@@ -96,7 +107,14 @@ def patch_class(text):
     rel = "dcrtpoly.h"
     text = once(text, '#include "utils/parallel.h"\n', '#include "utils/parallel.h"\n#include "pim/PimHook.h"\n', rel)
     text = once(text, "    std::vector<PolyType> m_vectors;\n", ACCESSORS, rel)
-    text = once(text, "m_vectors{e.m_vectors} {}", "m_vectors_{e.PimHostVectors()} {}", rel)
+    # copies of a resident poly copy the device buffer HBM to HBM instead of downloading it; the handle travels along
+    text = once(text, "m_vectors{e.m_vectors} {}",
+                "m_vectors_{}, pim{e.pim} { PimCopyFrom(e); }", rel)
+    text = once(text, "        m_format  = rhs.m_format;\n        m_vectors = rhs.m_vectors;\n        return *this;\n",
+                "        m_format  = rhs.m_format;\n        PimCopyFrom(rhs);\n"
+                "        if (rhs.pim) pim = rhs.pim;\n        return *this;\n", rel)
+    # FHE_B200_ATTACH=1: every DCRTPoly is born attached (pim/PimHook.h default_handle)
+    text = once(text, "    std::shared_ptr<PimManager> pim;\n", "    std::shared_ptr<PimManager> pim = pimhook::default_handle();\n", rel)
     text = once(text, "m_vectors{std::move(e.m_vectors)} {}",
                 "m_vectors_{std::move(e.m_vectors_)}, pimres_{std::move(e.pimres_)}, pim{std::move(e.pim)} {}", rel)
     # move assignment: take the device copy along instead of forcing a download
@@ -143,7 +161,7 @@ def patch_impl(text):
     # ---- the neighbouring methods: same pattern, device forms of csrc/automorph.cu and
     # csrc/basis.cu.  Each hook leaves the reference's own checks / exceptions to the CPU path (odd index, formats).
     auto_hook = ("\n    if (pim && (i & 1)%s) {\n"
-                 "        DCRTPolyImpl<VecType> dev(m_params, m_format, true);\n"
+                 "        DCRTPolyImpl<VecType> dev(m_params, m_format, false);\n"
                  "        if (pimhook::resident_automorphism(pim.get(), m_vectors_, pimres_, dev.m_vectors_, dev.pimres_, i,\n"
                  "                                           m_format == Format::EVALUATION ? 0 : 1)) {\n"
                  "            dev.pim = pim;\n"
@@ -170,6 +188,42 @@ def patch_impl(text):
                 "        return;\n"
                 "    }\n"
                 "    // TODO: move this inside loop if omp enabled\n    auto lastPoly(m_vectors.back());", rel)
+    # ModReduce (in place, either format): same shrink as DropLastElementAndScale
+    sig = ("                                      const std::vector<NativeInteger>& qlInvModqPrecon) {\n"
+           "    // TODO: move this inside loop if omp enabled\n    DCRTPolyImpl::PolyType delta(m_vectors.back());")
+    text = once(text, sig,
+                "                                      const std::vector<NativeInteger>& qlInvModqPrecon) {\n"
+                "    if (pim && m_vectors_.size() > 1) {\n"
+                "        auto full = pimhook::ensure_device(pim.get(), m_vectors_, pimres_);\n"
+                "        m_vectors_.resize(m_vectors_.size() - 1);\n"
+                "        DCRTPolyImpl::Params* newP = new DCRTPolyImpl::Params(*m_params);\n"
+                "        newP->PopLastParam();\n"
+                "        m_params.reset(newP);\n"
+                "        pimres_.reset();\n"
+                "        pimhook::resident_mod_reduce(pim.get(), full, m_vectors_, pimres_, t.ConvertToInt(),\n"
+                "                                     m_format == Format::EVALUATION ? 0 : 1);\n"
+                "        return;\n"
+                "    }\n"
+                "    // TODO: move this inside loop if omp enabled\n    DCRTPolyImpl::PolyType delta(m_vectors.back());", rel)
+    # ApproxModUp (in place: Q -> QP, result in EVALUATION format)
+    sig = ("                                        const std::vector<DoubleNativeInt>& modpBarrettMu) {\n"
+           "    std::vector<DCRTPolyImpl::PolyType> polyInNTT;\n")
+    text = once(text, sig,
+                "                                        const std::vector<DoubleNativeInt>& modpBarrettMu) {\n"
+                "    if (pim && !m_vectors_.empty() && m_vectors_.size() == paramsQ->GetParams().size() &&\n"
+                "        paramsQP->GetParams().size() == m_vectors_.size() + paramsP->GetParams().size()) {\n"
+                "        std::vector<DCRTPolyImpl::PolyType> shell;\n"
+                "        for (const auto& tp : paramsQP->GetParams()) shell.emplace_back(tp, Format::EVALUATION, false);\n"
+                "        std::shared_ptr<pimhook::Resident> up;\n"
+                "        if (pimhook::resident_mod_up(pim.get(), m_vectors_, pimres_, shell, up, m_format == Format::EVALUATION ? 0 : 1)) {\n"
+                "            m_vectors_ = std::move(shell);\n"
+                "            pimres_    = up;\n"
+                "            m_format   = Format::EVALUATION;\n"
+                "            m_params   = paramsQP;\n"
+                "            return;\n"
+                "        }\n"
+                "    }\n"
+                "    std::vector<DCRTPolyImpl::PolyType> polyInNTT;\n", rel)
     # ApproxSwitchCRTBasis (const, returns a polynomial over paramsP)
     sig = ("    const std::vector<std::vector<NativeInteger>>& QHatModp, const std::vector<DoubleNativeInt>& modpBarrettMu) const {\n"
            "#if defined(HAVE_INT128) && NATIVEINT == 64\n    DCRTPolyImpl<VecType> ans(paramsP, m_format, true);\n")
@@ -184,7 +238,7 @@ def patch_impl(text):
     text = once(text, sig,
                 "    if (pim && m_format == Format::EVALUATION && m_vectors_.size() > paramsP->GetParams().size()) {\n"
                 "        usint devQ = m_vectors_.size() - paramsP->GetParams().size();\n"
-                "        DCRTPolyImpl<VecType> dev(paramsQ, Format::EVALUATION, true);\n"
+                "        DCRTPolyImpl<VecType> dev(paramsQ, Format::EVALUATION, false);\n"
                 "        if (paramsQ->GetParams().size() > devQ)\n"
                 "            dev.DropLastElements(paramsQ->GetParams().size() - devQ);\n"
                 "        if (pimhook::resident_mod_down(pim.get(), m_vectors_, pimres_, devQ, t.ConvertToInt(), dev.m_vectors_, dev.pimres_)) {\n"

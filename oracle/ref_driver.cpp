@@ -203,7 +203,9 @@ ref_polys* ref_polys_binary(const ref_polys* a, const ref_polys* b, int op) {
     for (size_t i = 0; i < a->v.size(); i++) {
         if (op == 0) r->v.push_back(a->v[i].Plus(b->v[i]));
         else if (op == 1) r->v.push_back(a->v[i].Minus(b->v[i]));
-        else r->v.push_back(a->v[i].Times(b->v[i]));
+        else if (op == 2) r->v.push_back(a->v[i].Times(b->v[i]));
+        else if (op == 3) r->v.push_back(a->v[i]);                       // copy construction
+        else { DCRTPoly c; c = a->v[i]; r->v.push_back(std::move(c)); }  // copy assignment
     }
     return r;
 }

@@ -16,8 +16,7 @@ pytestmark = pytest.mark.skipif(not os.path.exists(HOOKED_SO), reason="oracle/_r
 vp, sz, ci, u32, u64 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint32, ctypes.c_uint64
 
 
-@pytest.fixture(scope="module")
-def hooked():
+def load_hooked():
     H = ctypes.CDLL(HOOKED_SO)
     H.ref_ctx_create.restype = vp
     H.ref_ctx_create.argtypes = [u32, u32, vp, vp]
@@ -43,11 +42,17 @@ def hooked():
     H.ref_polys_approx_switch.argtypes = [vp, vp]
     H.ref_polys_approx_mod_down.restype = vp
     H.ref_polys_approx_mod_down.argtypes = [vp, vp, vp, u64]
+    H.ref_polys_approx_mod_up.argtypes = [vp, vp, vp]
     H.ref_polys_serialize.restype = sz
     H.ref_polys_serialize.argtypes = [vp, sz, vp, sz]
     H.ref_polys_deserialize.restype = vp
     H.ref_polys_deserialize.argtypes = [vp, vp, sz]
     return H
+
+
+@pytest.fixture(scope="module")
+def hooked():
+    return load_hooked()
 
 
 def counters(H):
@@ -256,6 +261,50 @@ def test_resident_neighbouring_methods(hooked, oracle, pkg):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_resident_mod_up_and_mod_reduce(hooked, oracle, pkg, fmt):
+    """ApproxModUp and ModReduce through the live intercept: the hybrid key-switching core
+    ModUp(x) * k -> ModDown over the reference's own DCRTPoly stays in HBM (two uploads, one download), and BGV's
+    ModReduce keeps the format it was given.  Results equal the oracle's (which is pinned to the CPU path)."""
+    H = hooked
+    n, sq, sp, batch = 1 << 11, 3, 2, 2
+    q, psi = oracle.gen_params(60, n, sq + sp)
+    ob = oracle.basis(n, q, psi, sq)
+    oQP = oracle.ctx(n, q, psi)
+    mk = lambda a, b: H.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+    cQ, cP, cQP, cRest = mk(0, sq), mk(sq, sq + sp), mk(0, sq + sp), mk(0, sq - 1)
+    x = oracle.fill_ring(batch, n, q[:sq].copy(), 71)
+    k = oracle.fill_ring(batch, n, q, 72)
+    hx, hk = H.ref_polys_load(cQ, p(x), batch, fmt), H.ref_polys_load(cQP, p(k), batch, 0)
+    assert H.ref_polys_set_pim(hx, 1) == 0, H.ref_last_error()
+    up0, down0 = counters(H)
+    assert H.ref_polys_approx_mod_up(hx, cP, cQP) == 0, H.ref_last_error()      # Q -> QP, EVALUATION
+    assert H.ref_polys_format(hx) == 0
+    assert H.ref_polys_op(hx, hk, 2, 1) >= 0                                    # * key over QP
+    hd = H.ref_polys_approx_mod_down(hx, cQ, cP, 0)                             # QP -> Q
+    assert hd, H.ref_last_error()
+    assert counters(H) == (up0 + 2 * batch, down0)
+    want = ob.mod_down(oQP.elementwise(2, ob.mod_up(x, fmt), k), 0)
+    res = np.empty((batch, sq, n), np.uint64)
+    H.ref_polys_store(hd, p(res))
+    assert np.array_equal(res, want)
+    assert counters(H) == (up0 + 2 * batch, down0 + batch)
+    # ModReduce (t = 65537) on a resident operand in either format
+    y = oracle.fill_ring(batch, n, q[:sq].copy(), 73)
+    hy = H.ref_polys_load(cQ, p(y), batch, fmt)
+    assert H.ref_polys_set_pim(hy, 1) == 0
+    assert H.ref_polys_rescale(hy, cRest, 65537) == 0, H.ref_last_error()
+    assert H.ref_polys_format(hy) == fmt
+    res2 = np.empty((batch, sq - 1, n), np.uint64)
+    H.ref_polys_store(hy, p(res2))
+    assert np.array_equal(res2, oracle.rescale(n, q[:sq].copy(), psi[:sq].copy(), y, fmt, 65537))
+    for h in (hx, hk, hd, hy):
+        H.ref_polys_free(h)
+    for c in (cQ, cP, cQP, cRest):
+        H.ref_ctx_destroy(c)
+
+
+@pytest.mark.gpu
 def test_resident_poly_serialises_through_the_reference(hooked, oracle, pkg):
     """Serial::Serialize of the reference (DCRTPolyImpl::save, dcrtpoly.h:349-354) reads the towers through the const
     accessor, so a device-resident result is downloaded once and written in the wire format; the stream equals the one
@@ -290,3 +339,46 @@ def test_resident_poly_serialises_through_the_reference(hooked, oracle, pkg):
     for h in (ha, hb, hc):
         H.ref_polys_free(h)
     H.ref_ctx_destroy(ctx)
+
+
+def _attach_child():
+    """Runs in a fresh process with FHE_B200_ATTACH=1: no SetPim anywhere, yet the operators run on the device."""
+    from tests import oracle_py as op
+    H = load_hooked()
+    O = op.load()
+    up0, _ = counters(H)
+    run_ops(H, O, 1 << 12, 3, 2, pim_on=False)
+    # copies of an attached poly are device copies: a = polys[i]; a.SwitchFormat() as the reference's benchmark does
+    n, towers = 1 << 12, 3
+    q, psi = O.gen_params(60, n, towers)
+    x = O.fill_ring(1, n, q, 9)
+    ctx = H.ref_ctx_create(n, towers, p(q), p(psi))
+    hx = H.ref_polys_load(ctx, p(x), 1, 1)
+    up1, down1 = counters(H)
+    for _ in range(3):
+        hc = H.ref_polys_binary(hx, hx, 3 + _ % 2)    # op 3 / 4: copy construction / copy assignment of the first operand
+        assert hc, H.ref_last_error()
+        assert H.ref_polys_switch_format(hc, 1) >= 0
+        res = np.empty_like(x)
+        H.ref_polys_store(hc, p(res))
+        assert np.array_equal(res, O.ctx(n, q, psi).ntt(x, inverse=False))
+        H.ref_polys_free(hc)
+    up2, down2 = counters(H)
+    assert (up2 - up1, down2 - down1) == (1, 3), (up2 - up1, down2 - down1)   # the source went up once; each result came down once
+    H.ref_polys_store(hx, p(res))
+    assert np.array_equal(res, x)                     # the source itself is untouched
+    assert up2 > up0
+    print("attach-child ok")
+
+
+@pytest.mark.gpu
+def test_default_attach_runs_unmodified_callers_on_the_device():
+    """FHE_B200_ATTACH=1 (pim/PimHook.h default_handle): every DCRTPoly is born with the handle, so code that never calls
+    SetPim — the reference's own poly-benchmark-16k.cpp, tools/polybench.sh — runs its operators on the GPU."""
+    import subprocess
+    import sys
+    env = dict(os.environ, FHE_B200_ATTACH="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", "from tests import test_live_intercept as t; t._attach_child()"], cwd=root, env=env,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "attach-child ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
