@@ -483,6 +483,118 @@ inline bool resident_mod_reduce(PimManager *pim, const std::shared_ptr<Resident>
   return true;
 }
 
+/* the scheme's QHatInvModq (the table the caller passed in) against the one the cached plan derived from the moduli:
+ * a caller with other constants (another level's tables, a partial basis) stays on the CPU path */
+template <class IntVec>
+inline bool same_hat_inv(const CachedPlan<PimBasis> &plan, const IntVec &QHatInvModq, size_t sq, size_t sp) {
+  if (QHatInvModq.size() < sq) return false;
+  std::vector<uint64_t> hi(sq), hm(sq * sp);
+  if (fhe_basis_tables(plan.plan->handle(), hi.data(), hm.data()) != 0) return false;
+  for (size_t i = 0; i < sq; i++)
+    if (hi[i] != QHatInvModq[i].ConvertToInt()) return false;
+  return true;
+}
+
+/* DCRTPolyImpl::SwitchCRTBasis (dcrtpoly-impl.h:1178-1230, BFV, exact): a over Q -> out over P, same format */
+template <class Towers, class IntVec>
+inline bool resident_switch_exact(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
+                                  std::shared_ptr<Resident> &rout, const IntVec &QHatInvModq) {
+  if (!pim || a.empty() || out.empty()) return false;
+  auto da = ensure_device(pim, a, ra);
+  auto r = new_resident(pim, out);
+  auto plan = basis_for(da->ring, r->ring);
+  if (!same_hat_inv(plan, QHatInvModq, a.size(), out.size())) return false;
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_switch_crt_basis(plan.plan->handle(), r->d, da->d, 1, 0), "pim hook: exact basis switch");
+  }
+  finish(r->ctx);
+  rout = r;
+  return true;
+}
+
+/* DCRTPolyImpl::ExpandCRTBasis (dcrtpoly-impl.h:1311-1358, BFV): a over Q (either format) -> out over QP in
+ * result_format; `out` = host shells of the QP towers */
+template <class Towers, class IntVec>
+inline bool resident_expand(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
+                            std::shared_ptr<Resident> &rout, int format, int result_format, const IntVec &QHatInvModq) {
+  if (!pim || a.empty() || out.size() <= a.size()) return false;
+  auto da = ensure_device(pim, a, ra);
+  auto r = new_resident(pim, out);
+  const size_t sq = a.size(), sp = out.size() - sq;
+  static std::mutex mu;
+  static std::map<std::pair<PimRing *, size_t>, std::shared_ptr<PimRing>> views;
+  std::shared_ptr<PimRing> rp;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto key = std::make_pair(r->ring.get(), sq);
+    auto it = views.find(key);
+    if (it == views.end()) it = views.emplace(key, PimRing::View(r->ring, (uint32_t)sq, (uint32_t)sp)).first;
+    rp = it->second;
+  }
+  auto plan = basis_for(da->ring, rp);
+  if (!same_hat_inv(plan, QHatInvModq, sq, sp)) return false;
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_expand_crt_basis(plan.plan->handle(), r->d, da->d, 1, format, result_format, 0), "pim hook: expand basis");
+  }
+  finish(r->ctx);
+  rout = r;
+  return true;
+}
+
+/* DCRTPolyImpl::ScaleAndRound(paramsOutput, ...) (dcrtpoly-impl.h:1876-1960, BFV): a over QP -> out over the output
+ * basis (its first towers, or its last when out_last).  The plan is built from the scheme's own tables and cached by
+ * their address; a hit is checked against a copy of the fractions, so a table reallocated at the same address is caught. */
+template <class Towers, class Rows>
+inline bool resident_scale_round(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
+                                 std::shared_ptr<Resident> &rout, bool out_last, const std::vector<double> &frac, const Rows &modo) {
+  const size_t so = out.size();
+  if (!pim || a.empty() || so == 0 || so >= a.size() || frac.size() != a.size() - so || modo.size() != so) return false;
+  auto da = ensure_device(pim, a, ra);
+  struct Entry {
+    std::shared_ptr<PimScaleRound> plan;
+    std::shared_ptr<PlanLock> lock = std::make_shared<PlanLock>();
+    std::vector<double> frac;
+  };
+  static std::mutex mu;
+  static std::map<std::tuple<PimRing *, size_t, bool, const double *>, Entry> cache;
+  Entry e;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto key = std::make_tuple(da->ring.get(), so, out_last, frac.data());
+    auto it = cache.find(key);
+    if (it == cache.end() || it->second.frac != frac) {
+      std::vector<uint64_t> flat;
+      flat.reserve(so * (frac.size() + 1));
+      for (size_t j = 0; j < so; j++) {
+        if (modo[j].size() < frac.size() + 1) return false;
+        for (size_t i = 0; i <= frac.size(); i++) flat.push_back(modo[j][i].ConvertToInt());
+      }
+      Entry fresh;
+      fresh.plan = std::make_shared<PimScaleRound>(da->ring, (uint32_t)so, out_last, frac, flat);
+      fresh.frac = frac;
+      cache[key] = fresh;
+      it = cache.find(key);
+    }
+    e = it->second;
+  }
+  auto r = std::make_shared<Resident>();
+  r->ring = e.plan->Out();
+  r->ctx = pim->context();
+  r->towers = so;
+  r->n = da->n;
+  PimManager::check(fhe_alloc(r->ctx, r->towers * r->n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
+  r->device_newer = true;
+  {
+    std::lock_guard<std::mutex> lock(e.lock->mu);
+    PimManager::check(fhe_scale_and_round(e.plan->handle(), r->d, da->d, 1, 0), "pim hook: scale and round");
+  }
+  finish(r->ctx);
+  rout = r;
+  return true;
+}
+
 }  // namespace pimhook
 
 #endif /* _PIM_HOOK_ */

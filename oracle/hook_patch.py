@@ -233,6 +233,47 @@ def patch_impl(text):
                 "        ans.pim = pim;\n"
                 "        return ans;\n"
                 "    }\n", rel)
+    # BFV (HPS) set: SwitchCRTBasis (const), ExpandCRTBasis (in place), ScaleAndRound(paramsOutput, ...) (const)
+    sig = ("                                                            const std::vector<double>& qInv) const {\n"
+           "#if defined(HAVE_INT128) && NATIVEINT == 64\n    DCRTPolyImpl<VecType> ans(paramsP, m_format, true);\n")
+    text = once(text, sig, sig +
+                "    if (pim && pimhook::resident_switch_exact(pim.get(), m_vectors_, pimres_, ans.m_vectors_, ans.pimres_, QHatInvModq)) {\n"
+                "        ans.pim = pim;\n"
+                "        return ans;\n"
+                "    }\n", rel)
+    start = text.index("void DCRTPolyImpl<VecType>::ExpandCRTBasis(\n")
+    sig = ("    const std::vector<DoubleNativeInt>& modpBarrettMu, const std::vector<double>& qInv, Format resultFormat) {\n"
+           "    std::vector<DCRTPolyImpl::PolyType> polyInNTT;\n")
+    at = text.index(sig, start)
+    text = text[:at] + text[at:].replace(sig,
+                "    const std::vector<DoubleNativeInt>& modpBarrettMu, const std::vector<double>& qInv, Format resultFormat) {\n"
+                "    if (pim && !m_vectors_.empty() && paramsQP->GetParams().size() == m_vectors_.size() + paramsP->GetParams().size()) {\n"
+                "        std::vector<DCRTPolyImpl::PolyType> shell;\n"
+                "        for (const auto& tp : paramsQP->GetParams()) shell.emplace_back(tp, resultFormat, false);\n"
+                "        std::shared_ptr<pimhook::Resident> up;\n"
+                "        if (pimhook::resident_expand(pim.get(), m_vectors_, pimres_, shell, up, m_format == Format::EVALUATION ? 0 : 1,\n"
+                "                                     resultFormat == Format::EVALUATION ? 0 : 1, QHatInvModq)) {\n"
+                "            m_vectors_ = std::move(shell);\n"
+                "            pimres_    = up;\n"
+                "            m_format   = resultFormat;\n"
+                "            m_params   = paramsQP;\n"
+                "            return;\n"
+                "        }\n"
+                "    }\n"
+                "    std::vector<DCRTPolyImpl::PolyType> polyInNTT;\n", 1)
+    sig = ("    DCRTPolyImpl<VecType> ans(paramsOutput, m_format, true);\n"
+           "    usint ringDim      = m_params->GetRingDimension();\n")
+    text = once(text, sig,
+                "    DCRTPolyImpl<VecType> ans(paramsOutput, m_format, true);\n"
+                "    if (pim) {\n"
+                "        bool outLast = !(paramsOutput->GetParams()[0]->GetModulus() == m_params->GetParams()[0]->GetModulus());\n"
+                "        if (pimhook::resident_scale_round(pim.get(), m_vectors_, pimres_, ans.m_vectors_, ans.pimres_, outLast,\n"
+                "                                          tOSHatInvModsDivsFrac, tOSHatInvModsDivsModo)) {\n"
+                "            ans.pim = pim;\n"
+                "            return ans;\n"
+                "        }\n"
+                "    }\n"
+                "    usint ringDim      = m_params->GetRingDimension();\n", rel)
     # ApproxModDown (const, EVALUATION input over QP, returns a polynomial over Q)
     sig = ("    usint sizeQP = m_vectors.size();\n    usint sizeP  = paramsP->GetParams().size();\n    usint sizeQ  = sizeQP - sizeP;\n")
     text = once(text, sig,

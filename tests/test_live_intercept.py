@@ -43,6 +43,7 @@ def load_hooked():
     H.ref_polys_approx_mod_down.restype = vp
     H.ref_polys_approx_mod_down.argtypes = [vp, vp, vp, u64]
     H.ref_polys_approx_mod_up.argtypes = [vp, vp, vp]
+    H.ref_bfv_hps_mult.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp)]
     H.ref_polys_serialize.restype = sz
     H.ref_polys_serialize.argtypes = [vp, sz, vp, sz]
     H.ref_polys_deserialize.restype = vp
@@ -301,6 +302,52 @@ def test_resident_mod_up_and_mod_reduce(hooked, oracle, pkg, fmt):
     for h in (hx, hk, hd, hy):
         H.ref_polys_free(h)
     for c in (cQ, cP, cQP, cRest):
+        H.ref_ctx_destroy(c)
+
+
+@pytest.mark.gpu
+def test_resident_bfv_evalmult_core(hooked, oracle, pkg):
+    """The RNS core of BFVrns EvalMult (HPS; bfvrns-leveledshe.cpp:193-207, 322-356) written against the reference's own
+    DCRTPoly — ExpandCRTBasis x4, Times / +=, SetFormat, ScaleAndRound, SwitchCRTBasis — with the operands attached:
+    every step runs on the device (4 uploads and 3 downloads per ciphertext pair) and the three result polys equal the
+    same code on the CPU path bit for bit."""
+    H = hooked
+    n, sq, sr, batch, t = 1 << 11, 3, 4, 2, 65537
+    q, psi = oracle.gen_params(60, n, sq + sr)
+    mk = lambda a, b: H.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+    cQ, cR, cQR = mk(0, sq), mk(sq, sq + sr), mk(0, sq + sr)
+    data = [oracle.fill_ring(batch, n, q[:sq].copy(), 80 + k) for k in range(4)]
+
+    def run(attach):
+        hs = [H.ref_polys_load(cQ, p(d), batch, 0) for d in data]
+        if attach:
+            for h in hs:
+                assert H.ref_polys_set_pim(h, 1) == 0, H.ref_last_error()
+        outs = (vp * 3)()
+        c0 = counters(H)
+        assert H.ref_bfv_hps_mult(hs[0], hs[1], hs[2], hs[3], cR, cQR, t, outs) == 0, H.ref_last_error()
+        c1 = counters(H)
+        res = []
+        for k in range(3):
+            r = np.empty((batch, sq, n), np.uint64)
+            H.ref_polys_store(outs[k], p(r))
+            res.append(r)
+            H.ref_polys_free(outs[k])
+        c2 = counters(H)
+        for h in hs:
+            H.ref_polys_free(h)
+        return res, (c1[0] - c0[0], c1[1] - c0[1]), (c2[0] - c1[0], c2[1] - c1[1])
+
+    launches0 = pkg._native.lib.fhe_launch_count()
+    got, during, after = run(True)
+    assert pkg._native.lib.fhe_launch_count() - launches0 >= 20 * batch
+    assert during == (4 * batch, 0), during                 # operands go up once, nothing comes down during the product
+    assert after == (0, 3 * batch), after                   # the three result polys come down when they are read
+    want, cpu_during, _ = run(False)
+    assert cpu_during == (0, 0)
+    for k in range(3):
+        assert np.array_equal(got[k], want[k]), f"c{k}"
+    for c in (cQ, cR, cQR):
         H.ref_ctx_destroy(c)
 
 

@@ -115,12 +115,13 @@ class _DeviceWords:
         self.__cuda_array_interface__ = {"shape": (int(nwords),), "typestr": "<i8", "data": (int(dptr), False), "version": 2}
 
 
-def gather_device(dptr, nwords, dist, device):
+def gather_device(dptr, nwords, dist, device, out=None):
     """all-gather every rank's `nwords` result words, HBM to HBM over NCCL (NVLink / NVSwitch), without a host copy:
-    returns an int64 torch tensor [world][nwords] on `device`.  The caller synchronises its own stream first —
+    returns an int64 torch tensor [world][nwords] on `device` (`out`, when given, is reused as that tensor).  The caller synchronises its own stream first —
     torch enqueues the collective behind ITS current stream, not the C ABI's."""
     import torch
     src = torch.as_tensor(_DeviceWords(dptr, nwords), device=device)
-    out = torch.empty(dist.get_world_size() * int(nwords), dtype=torch.int64, device=device)
-    dist.all_gather_into_tensor(out, src)
+    if out is None:
+        out = torch.empty(dist.get_world_size() * int(nwords), dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(out.view(-1), src)
     return out.view(dist.get_world_size(), int(nwords))
