@@ -53,7 +53,7 @@ ACCESSORS = """
     /* B200 intercept, resident form (pim/PimHook.h): host view of the towers.  const: refresh from the device copy
      * if that is newer.  non-const: refresh, then drop the device copy (the caller may write). */
     const std::vector<PolyType>& PimHostVectors() const {
-        if (auto r = std::atomic_load(&pimres_)) pimhook::sync_host(m_vectors_, r, m_format);
+        if (pimres_) pimhook::sync_host(m_vectors_, pimres_, m_format);       /* one predictable branch: the reference reads m_vectors[i][j] in inner loops */
         return m_vectors_;
     }
     std::vector<PolyType>& PimHostVectors() {
@@ -224,23 +224,33 @@ def patch_impl(text):
                 "        }\n"
                 "    }\n"
                 "    std::vector<DCRTPolyImpl::PolyType> polyInNTT;\n", rel)
-    # ApproxSwitchCRTBasis (const, returns a polynomial over paramsP)
+    # ApproxSwitchCRTBasis (const, returns a polynomial over paramsP).  The hooks of the const methods sit BEFORE the
+    # reference's zero-initialised `ans` so that a device result costs no host allocation.
     sig = ("    const std::vector<std::vector<NativeInteger>>& QHatModp, const std::vector<DoubleNativeInt>& modpBarrettMu) const {\n"
            "#if defined(HAVE_INT128) && NATIVEINT == 64\n    DCRTPolyImpl<VecType> ans(paramsP, m_format, true);\n")
-    text = once(text, sig, sig +
-                "    if (pim && m_vectors_.size() <= paramsQ->GetParams().size() &&\n"
-                "        pimhook::resident_approx_switch(pim.get(), m_vectors_, pimres_, m_vectors_.size(), ans.m_vectors_, ans.pimres_)) {\n"
-                "        ans.pim = pim;\n"
-                "        return ans;\n"
-                "    }\n", rel)
+    text = once(text, sig,
+                "    const std::vector<std::vector<NativeInteger>>& QHatModp, const std::vector<DoubleNativeInt>& modpBarrettMu) const {\n"
+                "    if (pim && m_vectors_.size() <= paramsQ->GetParams().size()) {\n"
+                "        DCRTPolyImpl<VecType> dev(paramsP, m_format, false);\n"
+                "        if (pimhook::resident_approx_switch(pim.get(), m_vectors_, pimres_, m_vectors_.size(), dev.m_vectors_, dev.pimres_)) {\n"
+                "            dev.pim = pim;\n"
+                "            return dev;\n"
+                "        }\n"
+                "    }\n"
+                "#if defined(HAVE_INT128) && NATIVEINT == 64\n    DCRTPolyImpl<VecType> ans(paramsP, m_format, true);\n", rel)
     # BFV (HPS) set: SwitchCRTBasis (const), ExpandCRTBasis (in place), ScaleAndRound(paramsOutput, ...) (const)
     sig = ("                                                            const std::vector<double>& qInv) const {\n"
            "#if defined(HAVE_INT128) && NATIVEINT == 64\n    DCRTPolyImpl<VecType> ans(paramsP, m_format, true);\n")
-    text = once(text, sig, sig +
-                "    if (pim && pimhook::resident_switch_exact(pim.get(), m_vectors_, pimres_, ans.m_vectors_, ans.pimres_, QHatInvModq)) {\n"
-                "        ans.pim = pim;\n"
-                "        return ans;\n"
-                "    }\n", rel)
+    text = once(text, sig,
+                "                                                            const std::vector<double>& qInv) const {\n"
+                "    if (pim) {\n"
+                "        DCRTPolyImpl<VecType> dev(paramsP, m_format, false);\n"
+                "        if (pimhook::resident_switch_exact(pim.get(), m_vectors_, pimres_, dev.m_vectors_, dev.pimres_, QHatInvModq)) {\n"
+                "            dev.pim = pim;\n"
+                "            return dev;\n"
+                "        }\n"
+                "    }\n"
+                "#if defined(HAVE_INT128) && NATIVEINT == 64\n    DCRTPolyImpl<VecType> ans(paramsP, m_format, true);\n", rel)
     start = text.index("void DCRTPolyImpl<VecType>::ExpandCRTBasis(\n")
     sig = ("    const std::vector<DoubleNativeInt>& modpBarrettMu, const std::vector<double>& qInv, Format resultFormat) {\n"
            "    std::vector<DCRTPolyImpl::PolyType> polyInNTT;\n")
@@ -264,15 +274,16 @@ def patch_impl(text):
     sig = ("    DCRTPolyImpl<VecType> ans(paramsOutput, m_format, true);\n"
            "    usint ringDim      = m_params->GetRingDimension();\n")
     text = once(text, sig,
-                "    DCRTPolyImpl<VecType> ans(paramsOutput, m_format, true);\n"
                 "    if (pim) {\n"
                 "        bool outLast = !(paramsOutput->GetParams()[0]->GetModulus() == m_params->GetParams()[0]->GetModulus());\n"
-                "        if (pimhook::resident_scale_round(pim.get(), m_vectors_, pimres_, ans.m_vectors_, ans.pimres_, outLast,\n"
+                "        DCRTPolyImpl<VecType> dev(paramsOutput, m_format, false);\n"
+                "        if (pimhook::resident_scale_round(pim.get(), m_vectors_, pimres_, dev.m_vectors_, dev.pimres_, outLast,\n"
                 "                                          tOSHatInvModsDivsFrac, tOSHatInvModsDivsModo)) {\n"
-                "            ans.pim = pim;\n"
-                "            return ans;\n"
+                "            dev.pim = pim;\n"
+                "            return dev;\n"
                 "        }\n"
                 "    }\n"
+                "    DCRTPolyImpl<VecType> ans(paramsOutput, m_format, true);\n"
                 "    usint ringDim      = m_params->GetRingDimension();\n", rel)
     # ApproxModDown (const, EVALUATION input over QP, returns a polynomial over Q)
     sig = ("    usint sizeQP = m_vectors.size();\n    usint sizeP  = paramsP->GetParams().size();\n    usint sizeQ  = sizeQP - sizeP;\n")
