@@ -293,3 +293,45 @@ def test_bfv_hps_mult_core_reference_golden(pkg, backend, oracle, case):
     mult.close()
     d.close()
     ring.close()
+
+
+@pytest.mark.parametrize("wide", [False, True], ids=["split30", "mac128"])
+@pytest.mark.parametrize("n,sq,sp,batch", [(256, 33, 11, 2), (512, 17, 20, 1), (128, 40, 7, 1), (64, 8, 10, 2),
+                                           (64, 9, 30, 1)])
+def test_basis_accumulate_forms_many_towers(pkg, backend, oracle, monkeypatch, wide, n, sq, sp, batch):
+    """Both accumulate forms of basis_switch_kernel / scale_round_kernel (carry-free 30-bit split limbs, normalised every
+    8 terms; 128-bit multiply-accumulate, FHE_B200_BASIS_WIDE=1) with more source towers than one normalisation period,
+    odd and even counts, every column-block width, and the largest operands the moduli allow."""
+    if wide:
+        monkeypatch.setenv("FHE_B200_BASIS_WIDE", "1")
+    else:
+        monkeypatch.delenv("FHE_B200_BASIS_WIDE", raising=False)
+    q, psi, ring, rq, rp, ob = setup(pkg, backend, oracle, 60, n, sq, sp)
+    d = Dev(backend)
+    q2p = pkg.Basis(rq, rp)
+    x = oracle.fill_ring(batch, n, q[:sq].copy(), 301)
+    x[0, :, 0] = q[:sq] - 1
+    x[0, :, 1] = 0
+    x[0, :, 2] = 1
+    dx, dp = d.put(x), d.new(batch * sp * n)
+    q2p.approx_switch(dp, dx, batch)
+    assert np.array_equal(backend.d2h(dp, batch * sp * n).reshape(batch, sp, n), ob.approx_switch(x))
+    q2p.switch_crt_basis(dp, dx, batch)
+    assert np.array_equal(backend.d2h(dp, batch * sp * n).reshape(batch, sp, n), ob.switch_exact(x))
+    # ScaleAndRound: the inputs themselves are the factors; tables at their largest values
+    rng = np.random.default_rng(sq * 100 + sp)
+    frac = rng.random(sq)
+    modr = np.stack([rng.integers(0, int(m), size=sq + 1, dtype=np.uint64) for m in q[sq:]])
+    modr[:, ::2] = (q[sq:] - 1)[:, None]
+    plan = pkg.ScaleRound(ring, sp, frac, modr, out_last=True)
+    y = oracle.fill_ring(batch, n, q, 302)
+    y[0, :, 0] = q - 1
+    y[0, :, 1] = q - 1
+    y[0, :, 2] = 0
+    dy, out = d.put(y), d.new(batch * sp * n)
+    plan.scale_and_round(out, dy, batch)
+    assert np.array_equal(backend.d2h(out, batch * sp * n).reshape(batch, sp, n), ob.scale_and_round(y, frac, modr, 1))
+    for o in (plan, q2p, rq, rp):
+        o.close()
+    d.close()
+    ring.close()

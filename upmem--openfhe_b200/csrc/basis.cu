@@ -7,20 +7,22 @@
 //   NativeVectorT::SwitchModulus           math/hal/intnat/mubintvecnat.cpp:112-135
 //
 // basis_switch_kernel: one thread per coefficient index.  For each source tower i it forms
-// y_i = x_i * [(Q/q_i)^-1]_{q_i} mod q_i (Shoup, canonical) and accumulates y_i * [Q/q_i]_{p_j} into 128-bit sums for
-// JT target towers at a time (IMAD.WIDE chains with carry), then reduces each sum modulo p_j with the reference's
-// 128-by-64 Barrett step.  Every value stored is the canonical residue the CPU path produces.  The [Q/q_i]_{p_j}
-// slice, the Shoup constants and the moduli sit in shared memory.  Integer-pipe bound: 4 IMAD.WIDE per (i, j) pair
-// per coefficient; HBM traffic is 8 B per source tower and 8 B per target tower per coefficient.
+// y_i = x_i * [(Q/q_i)^-1]_{q_i} mod q_i (Shoup, canonical) and accumulates y_i * [Q/q_i]_{p_j} for up to ten target
+// towers at a time - carry-free on 30-bit halves, three 32x32 multiplies per product (Acc30 / mac_group below; the
+// 128-bit multiply-accumulate form mac128 serves tables with entries of 2^60 and more) - then reduces each sum modulo p_j
+// (reduce128).  Every value stored is the canonical residue the CPU path produces.  The [Q/q_i]_{p_j} slice, the Shoup
+// constants and the moduli sit in shared memory.  Integer-pipe bound: 3 IMAD.WIDE per (i, j) pair per coefficient; HBM
+// traffic is 8 B per source tower and 8 B per target tower per coefficient.
 // tower_affine_kernel / rescale_spread_kernel: one pass, 128-bit loads and stores, HBM-bound.
+#include <stdlib.h>
 #include "modarith.cuh"
 #include "kernels.h"
 
 namespace fhe {
 
-// acc += a * b on a 128-bit accumulator.  Written with unsigned __int128 so that ptxas emits the four 32x32 partial
-// products once (4 IMAD.WIDE.U32 with carry chains); the mad.lo.cc / madc.hi PTX pair recomputes the low product
-// (about 6 wide multiplies per MAC, measured with tools/sass_mix.py).
+// acc += a * b on a 128-bit accumulator (the general form, any 64-bit factors).  Written with unsigned __int128 so that
+// ptxas emits the four 32x32 partial products once (4 IMAD.WIDE.U32 with carry chains); the mad.lo.cc / madc.hi PTX pair
+// recomputes the low product (about 6 wide multiplies per MAC, measured with tools/sass_mix.py).
 __device__ __forceinline__ void mac128(u64& lo, u64& hi, u64 a, u64 b) {
     unsigned __int128 acc = ((unsigned __int128)hi << 64) | lo;
     acc += (unsigned __int128)a * b;
@@ -28,17 +30,19 @@ __device__ __forceinline__ void mac128(u64& lo, u64& hi, u64 a, u64 b) {
     hi = (u64)(acc >> 64);
 }
 
-// utils/utilities-int.h:60-110: a mod m for a 128-bit a with mu = floor(2^128 / m)
-__device__ __forceinline__ u64 barrett128(u64 a_lo, u64 a_hi, u64 m, u64 mu_lo, u64 mu_hi) {
-    u64 left_hi = __umul64hi(a_lo, mu_lo);
-    u64 mlo = a_lo * mu_hi, mhi = __umul64hi(a_lo, mu_hi);
-    u64 tmp1 = mlo + left_hi;
-    u64 tmp2 = mhi + (tmp1 < mlo ? 1ull : 0ull);
-    u64 m2lo = a_hi * mu_lo, m2hi = __umul64hi(a_hi, mu_lo);
-    u64 left2 = m2hi + ((u64)(m2lo + tmp1) < m2lo ? 1ull : 0ull);
-    u64 t = a_hi * mu_hi + tmp2 + left2;
-    u64 r = a_lo - t * m;
-    while (r >= m) r -= m;
+// (hi * 2^64 + lo) mod p, canonical - the value BarrettUint128ModUint64 (utils/utilities-int.h:60-110) returns, by a
+// cheaper route than its three 64x64 products against floor(2^128/p): with c = 2^64 mod p the sum is congruent to
+// hi * c + lo, and both parts take a one-word quotient estimate (Shoup's for hi * c with c' = floor(c * 2^64 / p); the
+// same with the constant 1 for lo, floor(2^64 / p)), each short by at most one, so
+// hi * c + lo - (mulhi(hi, c') + mulhi(lo, pinv)) * p is in [0, 4p) and only its low 64 bits are ever formed.
+// 2 high products + 2 low ones instead of ~5 full ones; no loop.  Needs p < 2^62.
+struct TargetMod { u64 p, c64, c64p, pinv, post, postp; };
+__device__ __forceinline__ u64 reduce128(u64 lo, u64 hi, const TargetMod& t) {
+    u64 qh = __umul64hi(hi, t.c64p) + __umul64hi(lo, t.pinv);
+    u64 r = lo + hi * t.c64 - qh * t.p;
+    u64 p2 = t.p << 1;
+    if (r >= p2) r -= p2;
+    if (r >= t.p) r -= t.p;
     return r;
 }
 
@@ -52,24 +56,132 @@ __device__ __forceinline__ u64 switch_modulus(u64 v, u64 half, u64 nm, u64 diff,
     return v;
 }
 
-constexpr int BS_THREADS = 256;
+#ifndef FHE_BS_THREADS
+#define FHE_BS_THREADS 128
+#endif
+constexpr int BS_THREADS = FHE_BS_THREADS;
+constexpr int BS_JT_MAX = 10;                  // target towers accumulated per thread (8 registers each in the split form)
 
-// EXACT: DCRTPolyImpl::SwitchCRTBasis (dcrtpoly-impl.h:1178-1230): additionally counts the q-overflows
-// alpha = (unsigned)(0.5 + sum_i double(y_i) * qinv[i]) in IEEE double (round-to-nearest multiply and add, in index
-// order, never fused — what the CPU path computes) and subtracts [alpha*Q]_{p_j}.
-template <int JT, bool EXACT>
-__global__ void __launch_bounds__(BS_THREADS)
+// Carry-free form of the same sum for operands below 2^60 (every modulus on this path is, basicint.h:44-45; the host
+// checks the tables and picks the mac128 form otherwise).  Both factors are cut at bit 30: y = y0 + y1 * 2^30,
+// h = h0 + h1 * 2^30, and the product is taken Karatsuba-wise from THREE 32x32 multiplies, y0*h0, y1*h1 and
+// (y0+y1)*(h0+h1) (the sums are below 2^31, the product below 2^62).  Up to four source towers are summed through the
+// multiplier's own 64-bit addend (IMAD.WIDE chains that start from zero: 4 * 2^62 fits), then the middle term is
+// recovered with two subtractions and the three partial sums join the running limbs a0 (weight 1), a1 (2^30), a2 (2^60)
+// with plain 64-bit adds - no 128-bit carry chain anywhere.  The limbs hold 8 terms between normalisations
+// (a1 takes less than 2^61 per term: 8 * 2 * (2^30-1)^2 + 2^34 + 2^30 < 2^64); normalise() pushes the bits above 30 of
+// each limb into the next one, a3 collects everything from bit 90 up (the whole sum is below 2^128).
+constexpr u32 M30 = (1u << 30) - 1;
+#ifndef FHE_MINB
+#define FHE_MINB 4
+#endif
+struct Acc30 {
+    u64 a0, a1, a2, a3;
+    __device__ __forceinline__ void clear() { a0 = a1 = a2 = a3 = 0; }
+    __device__ __forceinline__ void normalise() {
+        a1 += a0 >> 30; a0 &= M30;
+        a2 += a1 >> 30; a1 &= M30;
+        a3 += a2 >> 30; a2 &= M30;
+    }
+    __device__ __forceinline__ void value(u64& lo, u64& hi) {      // after normalise()
+        lo = a0 | (a1 << 30) | (a2 << 60);
+        hi = (a2 >> 4) | (a3 << 26);
+    }
+};
+// value below 2^60 -> its low and high 30 bits, in 32-bit operations only (a 64-bit shift followed by a truncation makes
+// ptxas carry a dead high word through every product that uses the result)
+__device__ __forceinline__ void split30(u64 y, u32& y0, u32& y1) {
+    u32 l, h;
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(l), "=r"(h) : "l"(y));
+    y0 = l & M30;
+    y1 = __funnelshift_r(l, h, 30);
+}
+// table entry in shared memory, split form: {h0, h1, h0 + h1, -}
+__device__ __forceinline__ uint4 pack30(u64 h) {
+    u32 h0 = (u32)h & M30, h1 = (u32)(h >> 30);
+    return make_uint4(h0, h1, h0 + h1, 0u);
+}
+// acc[jj] += sum_g y[g] * h[g][jj] for G <= 4 source towers and JT target towers; hr = [G][JT] entries
+template <int G, int JT>
+__device__ __forceinline__ void mac_group(Acc30 (&acc)[JT], const u64 (&y)[G], const uint4* __restrict__ hr) {
+    static_assert(G >= 1 && G <= 4, "the middle products of more than four terms overflow 64 bits");
+    u32 y0[G], y1[G], ys[G];
+#pragma unroll
+    for (int g = 0; g < G; g++) {
+        split30(y[g], y0[g], y1[g]);
+        ys[g] = y0[g] + y1[g];
+    }
+#pragma unroll
+    for (int jj = 0; jj < JT; jj++) {
+        u64 t0 = 0, t2 = 0, tm = 0;
+#pragma unroll
+        for (int g = 0; g < G; g++) {
+            const uint4 h = hr[g * JT + jj];
+            t0 += (u64)y0[g] * h.x;
+            t2 += (u64)y1[g] * h.y;
+            tm += (u64)ys[g] * h.z;
+        }
+        acc[jj].a0 += t0;
+        acc[jj].a1 += tm - t0 - t2;
+        acc[jj].a2 += t2;
+    }
+}
+// All sq source towers: groups of four, then two, then one.  load(i) fetches the coefficient of tower i, mul(i, x) turns
+// it into the multiplier (the Shoup product for the basis switch, the coefficient itself for ScaleAndRound).  The loads
+// of the next group are issued before the multiplies of the current one.
+template <int JT, class L, class F>
+__device__ __forceinline__ void mac_towers(Acc30 (&acc)[JT], u32 sq, const uint4* __restrict__ sH, L&& load, F&& mul) {
+    u64 xv[4];
+#pragma unroll
+    for (int g = 0; g < 4; g++) xv[g] = (u32)g < sq ? load(g) : 0ull;
+    u32 i = 0;
+    for (; i + 4 <= sq; i += 4) {
+        u64 y[4];
+#pragma unroll
+        for (int g = 0; g < 4; g++) y[g] = mul(i + g, xv[g]);
+#pragma unroll
+        for (int g = 0; g < 4; g++) xv[g] = i + 4 + g < sq ? load(i + 4 + g) : 0ull;
+        mac_group<4, JT>(acc, y, sH + (size_t)i * JT);
+        if (i & 4) {
+#pragma unroll
+            for (int jj = 0; jj < JT; jj++) acc[jj].normalise();
+        }
+    }
+    if (i + 2 <= sq) {
+        const u64 y[2] = {mul(i, xv[0]), mul(i + 1, xv[1])};
+        mac_group<2, JT>(acc, y, sH + (size_t)i * JT);
+        i += 2;
+        xv[0] = xv[2];
+    }
+    if (i < sq) {
+        const u64 y[1] = {mul(i, xv[0])};
+        mac_group<1, JT>(acc, y, sH + (size_t)i * JT);
+    }
+#pragma unroll
+    for (int jj = 0; jj < JT; jj++) acc[jj].normalise();
+}
+
+template <int JT, bool EXACT, bool SPLIT>
+__global__ void __launch_bounds__(BS_THREADS, SPLIT ? FHE_MINB : 2 * FHE_MINB)
 basis_switch_kernel(u64* __restrict__ dst, const u64* __restrict__ src, size_t items, u32 logN, BasisDev bd,
                     u32 srcT, u32 src0, u32 dstT, u32 dst0) {
     extern __shared__ __align__(16) u64 sm[];
-    u64* sH = sm;                                          // [sq][JT]
-    u64* sQ = sH + (size_t)bd.sq * JT;                     // [sq]
+    constexpr int HW = SPLIT ? 2 : 1;                      // words per table entry
+    u64* sH = sm;                                          // [sq][JT] (split form: uint4 {h0, h1, h0+h1, -})
+    u64* sQ = sH + (size_t)bd.sq * JT * HW;                // [sq]
     u64* sC = sQ + bd.sq;                                  // [sq][2] {c, companion}
     double* sI = reinterpret_cast<double*>(sC + 2 * bd.sq); // [sq] 1/q_i (EXACT only)
+    TargetMod* sT = reinterpret_cast<TargetMod*>(sI + bd.sq); // [JT]
     const u32 j0 = blockIdx.y * JT;
+    if (threadIdx.x < JT && j0 + threadIdx.x < bd.sp) {
+        const BasisTarget g = bd.tgt[j0 + threadIdx.x];
+        sT[threadIdx.x] = TargetMod{g.p, g.c64, g.c64p, g.pinv, g.post, g.postp};
+    }
     for (u32 k = threadIdx.x; k < bd.sq * JT; k += BS_THREADS) {
         u32 i = k / JT, jj = k % JT;
-        sH[k] = (j0 + jj < bd.sp) ? bd.hat[(size_t)i * bd.sp + j0 + jj] : 0ull;
+        u64 h = (j0 + jj < bd.sp) ? bd.hat[(size_t)i * bd.sp + j0 + jj] : 0ull;
+        if (SPLIT) reinterpret_cast<uint4*>(sH)[k] = pack30(h);
+        else sH[k] = h;
     }
     for (u32 i = threadIdx.x; i < bd.sq; i += BS_THREADS) {
         sQ[i] = bd.q[i];
@@ -78,33 +190,97 @@ basis_switch_kernel(u64* __restrict__ dst, const u64* __restrict__ src, size_t i
         if (EXACT) sI[i] = bd.qinv[i];
     }
     __syncthreads();
-    const size_t e = (size_t)blockIdx.x * BS_THREADS + threadIdx.x;
-    if (e >= items) return;
-    const size_t b = e >> logN;
-    const u32 n = (u32)e & ((1u << logN) - 1);
-    u64 lo[JT], hi[JT];
+    // a CTA walks over coefficient tiles: the tables above are staged once for all of them
+    for (size_t e = (size_t)blockIdx.x * BS_THREADS + threadIdx.x; e < items; e += (size_t)gridDim.x * BS_THREADS) {
+        const size_t b = e >> logN;
+        const u32 n = (u32)e & ((1u << logN) - 1);
+        const u64* sp = src + (((b * srcT) + src0) << logN) + n;
+        u64 lo[JT], hi[JT];
+        double nu = 0.5;
+        // multiplier of source tower i: y_i = x_i * [(Q/q_i)^-1]_{q_i} mod q_i, canonical (:1056-1058)
+        auto load = [&](u32 i) -> u64 { return sp[(size_t)i << logN]; };
+        auto term = [&](u32 i, u64 x) -> u64 {
+            u64 y = shoup(x, sC[2 * i], sC[2 * i + 1], sQ[i]);
+            if (EXACT) nu = __dadd_rn(nu, __dmul_rn(__ull2double_rn(y), sI[i]));
+            return y;
+        };
+        if constexpr (SPLIT) {
+            Acc30 acc[JT];
 #pragma unroll
-    for (int jj = 0; jj < JT; jj++) { lo[jj] = 0; hi[jj] = 0; }
-    const u64* sp = src + (((b * srcT) + src0) << logN) + n;
-    u64 x = sp[0];
-    double nu = 0.5;
-    for (u32 i = 0; i < bd.sq; i++) {
-        u64 xn = (i + 1 < bd.sq) ? sp[(size_t)(i + 1) << logN] : 0ull;     // prefetch the next tower's coefficient
-        u64 y = shoup(x, sC[2 * i], sC[2 * i + 1], sQ[i]);
-        if (EXACT) nu = __dadd_rn(nu, __dmul_rn(__ull2double_rn(y), sI[i]));
+            for (int jj = 0; jj < JT; jj++) acc[jj].clear();
+            mac_towers<JT>(acc, bd.sq, reinterpret_cast<const uint4*>(sH), load, term);
 #pragma unroll
-        for (int jj = 0; jj < JT; jj++) mac128(lo[jj], hi[jj], y, sH[i * JT + jj]);
-        x = xn;
+            for (int jj = 0; jj < JT; jj++) acc[jj].value(lo[jj], hi[jj]);
+        } else {
+#pragma unroll
+            for (int jj = 0; jj < JT; jj++) { lo[jj] = 0; hi[jj] = 0; }
+            u64 x = sp[0];
+            for (u32 i = 0; i < bd.sq; i++) {
+                u64 xn = (i + 1 < bd.sq) ? sp[(size_t)(i + 1) << logN] : 0ull;     // prefetch the next tower's coefficient
+                u64 y = shoup(x, sC[2 * i], sC[2 * i + 1], sQ[i]);
+                if (EXACT) nu = __dadd_rn(nu, __dmul_rn(__ull2double_rn(y), sI[i]));
+#pragma unroll
+                for (int jj = 0; jj < JT; jj++) mac128(lo[jj], hi[jj], y, sH[i * JT + jj]);
+                x = xn;
+            }
+        }
+        const u32 alpha = EXACT ? (u32)nu : 0u;
+#pragma unroll
+        for (int jj = 0; jj < JT; jj++) {
+            if (j0 + jj < bd.sp) {
+                const TargetMod tg = sT[jj];
+                u64 r = reduce128(lo[jj], hi[jj], tg);
+                if (tg.post) r = shoup(r, tg.post, tg.postp, tg.p);
+                if (EXACT) r = submod(r, bd.alphaq[(size_t)alpha * bd.sp + j0 + jj], tg.p);
+                dst[(((b * dstT) + dst0 + j0 + jj) << logN) + n] = r;
+            }
+        }
     }
-    const u32 alpha = EXACT ? (u32)nu : 0u;
-#pragma unroll
-    for (int jj = 0; jj < JT; jj++) {
-        if (j0 + jj < bd.sp) {
-            const BasisTarget tg = bd.tgt[j0 + jj];
-            u64 r = barrett128(lo[jj], hi[jj], tg.p, tg.mu_lo, tg.mu_hi);
-            if (tg.post) r = shoup(r, tg.post, tg.postp, tg.p);
-            if (EXACT) r = submod(r, bd.alphaq[(size_t)alpha * bd.sp + j0 + jj], tg.p);
-            dst[(((b * dstT) + dst0 + j0 + jj) << logN) + n] = r;
+}
+
+// Grid: a few waves of CTAs (SMs x resident CTAs of this kernel), shared between the column blocks; every CTA stages
+// the tables once and walks over its coefficient tiles.  Eight waves measured best on the B200 (one wave leaves the SMs
+// in lock step, one tile per CTA pays the table staging per tile); FHE_B200_BASIS_WAVES overrides (tuning only).
+static int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e && *e ? atoi(e) : dflt;
+}
+template <class K>
+static unsigned persistent_grid_x(K kernel, size_t smem, size_t tiles, int nblk) {
+    static const int waves = env_int("FHE_B200_BASIS_WAVES", 8);
+    int dev = 0, sms = 148, occ = 1;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, BS_THREADS, smem) != cudaSuccess || occ < 1) occ = 1;
+    size_t cap = (size_t)sms * occ * (waves > 0 ? waves : 1) / nblk;
+    if (cap < 1) cap = 1;
+    return (unsigned)(tiles < cap ? tiles : cap);
+}
+// Column blocking: as few blocks of target towers as the accumulator registers allow, all of (nearly) the same width, so
+// that no thread accumulates padding columns (sp = 10 runs as one block of 10, sp = 30 as three of 10, sp = 17 as 9 + 8).
+static void column_blocks(uint32_t sp, bool narrow, int& jt, int& nblk) {
+    static const int jenv = env_int("FHE_B200_BASIS_JT", 0);
+    int jmax = narrow ? BS_JT_MAX : 8;
+    if (jenv >= 1 && jenv < jmax) jmax = jenv;
+    nblk = (int)(sp + jmax - 1) / jmax;
+    jt = (int)(sp + nblk - 1) / nblk;
+}
+
+template <int JT, bool EXACT>
+static void launch_basis_switch_jt(int jt, bool split, int nblk, size_t smem, cudaStream_t st, u64* d, const u64* s, size_t items,
+                                   u32 logN, const BasisDev& bd, u32 srcT, u32 src0, u32 dstT, u32 dst0) {
+    if constexpr (JT >= 1) {
+        if (jt == JT) {
+            const size_t tiles = (items + BS_THREADS - 1) / BS_THREADS;
+            if (split) {
+                auto k = basis_switch_kernel<JT, EXACT, true>;
+                k<<<dim3(persistent_grid_x(k, smem, tiles, nblk), nblk), BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0);
+            } else {
+                auto k = basis_switch_kernel<(JT > 8 ? 8 : JT), EXACT, false>;
+                k<<<dim3(persistent_grid_x(k, smem, tiles, nblk), nblk), BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0);
+            }
+        } else {
+            launch_basis_switch_jt<JT - 1, EXACT>(jt, split, nblk, smem, st, d, s, items, logN, bd, srcT, src0, dstT, dst0);
         }
     }
 }
@@ -112,15 +288,11 @@ basis_switch_kernel(u64* __restrict__ dst, const u64* __restrict__ src, size_t i
 template <bool EXACT>
 static cudaError_t launch_basis_switch_t(const BasisDev& bd, u64* d, uint32_t dstT, uint32_t dst0, const u64* s, uint32_t srcT,
                                          uint32_t src0, size_t items, uint32_t logN, cudaStream_t st) {
-    int jt = bd.sp >= 8 ? 8 : bd.sp >= 4 ? 4 : bd.sp >= 2 ? 2 : 1;
-    dim3 grid((unsigned)((items + BS_THREADS - 1) / BS_THREADS), (bd.sp + jt - 1) / jt);
-    size_t smem = ((size_t)bd.sq * jt + 4 * (size_t)bd.sq) * 8;
-    switch (jt) {
-        case 8: basis_switch_kernel<8, EXACT><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0); break;
-        case 4: basis_switch_kernel<4, EXACT><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0); break;
-        case 2: basis_switch_kernel<2, EXACT><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0); break;
-        default: basis_switch_kernel<1, EXACT><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, bd, srcT, src0, dstT, dst0); break;
-    }
+    int jt, nblk;
+    column_blocks(bd.sp, bd.narrow != 0, jt, nblk);
+    nblk = (int)(bd.sp + jt - 1) / jt;
+    size_t smem = ((size_t)bd.sq * jt * (bd.narrow ? 2 : 1) + 4 * (size_t)bd.sq) * 8 + (size_t)jt * sizeof(TargetMod);
+    launch_basis_switch_jt<BS_JT_MAX, EXACT>(jt, bd.narrow != 0, nblk, smem, st, d, s, items, logN, bd, srcT, src0, dstT, dst0);
     kernel_launch_count_add(1);
     return cudaGetLastError();
 }
@@ -139,54 +311,104 @@ cudaError_t launch_basis_switch(const BasisDev& bd, uint64_t* dst, uint32_t dstT
 // in0 / out0 = first input / output tower.  Per coefficient: nu = 0.5 + sum_i frac[i] * double(x_i) (IEEE double, in
 // order, not fused), alpha = integer part of nu (64-bit, or 128-bit when nu >= 2^64), and for every output modulus o_j:
 // (sum_i x_i * modo[j][i] + x_out_j * modo[j][sI]) mod o_j + alpha mod o_j.
-template <int JT>
-__global__ void __launch_bounds__(BS_THREADS)
+template <int JT, bool SPLIT>
+__global__ void __launch_bounds__(BS_THREADS, SPLIT ? FHE_MINB : 2 * FHE_MINB)
 scale_round_kernel(u64* __restrict__ dst, const u64* __restrict__ src, size_t items, u32 logN, ScaleDev sd) {
     extern __shared__ __align__(16) u64 sm[];
-    u64* sM = sm;                                               // [sI+1][JT]
-    double* sF = reinterpret_cast<double*>(sM + (size_t)(sd.sI + 1) * JT);   // [sI]
+    constexpr int HW = SPLIT ? 2 : 1;                           // words per table entry
+    u64* sM = sm;                                               // [sI+1][JT] (split form: uint4 {h0, h1, h0+h1, -})
+    double* sF = reinterpret_cast<double*>(sM + (size_t)(sd.sI + 1) * JT * HW);   // [sI]
+    TargetMod* sT = reinterpret_cast<TargetMod*>(sF + sd.sI);                // [JT]
     const u32 j0 = blockIdx.y * JT;
+    if (threadIdx.x < JT && j0 + threadIdx.x < sd.sO) {
+        const BasisTarget g = sd.tgt[j0 + threadIdx.x];
+        sT[threadIdx.x] = TargetMod{g.p, g.c64, g.c64p, g.pinv, g.post, g.postp};
+    }
     for (u32 k = threadIdx.x; k < (sd.sI + 1) * JT; k += BS_THREADS) {
         u32 i = k / JT, jj = k % JT;
-        sM[k] = (j0 + jj < sd.sO) ? sd.modo[(size_t)(j0 + jj) * (sd.sI + 1) + i] : 0ull;
+        u64 h = (j0 + jj < sd.sO) ? sd.modo[(size_t)(j0 + jj) * (sd.sI + 1) + i] : 0ull;
+        if (SPLIT) reinterpret_cast<uint4*>(sM)[k] = pack30(h);
+        else sM[k] = h;
     }
     for (u32 i = threadIdx.x; i < sd.sI; i += BS_THREADS) sF[i] = sd.frac[i];
     __syncthreads();
-    const size_t e = (size_t)blockIdx.x * BS_THREADS + threadIdx.x;
-    if (e >= items) return;
-    const size_t b = e >> logN;
-    const u32 n = (u32)e & ((1u << logN) - 1);
-    const u32 T = sd.sI + sd.sO;
-    u64 lo[JT], hi[JT];
+    for (size_t e = (size_t)blockIdx.x * BS_THREADS + threadIdx.x; e < items; e += (size_t)gridDim.x * BS_THREADS) {
+        const size_t b = e >> logN;
+        const u32 n = (u32)e & ((1u << logN) - 1);
+        const u32 T = sd.sI + sd.sO;
+        const u64* ip = src + (((b * T) + sd.in0) << logN) + n;
+        u64 lo[JT], hi[JT];
+        double nu = 0.5;
+        auto load = [&](u32 i) -> u64 { return ip[(size_t)i << logN]; };
+        auto term = [&](u32 i, u64 x) -> u64 {
+            nu = __dadd_rn(nu, __dmul_rn(sF[i], __ull2double_rn(x)));
+            return x;
+        };
+        Acc30 acc[SPLIT ? JT : 1];
+        if constexpr (SPLIT) {
 #pragma unroll
-    for (int jj = 0; jj < JT; jj++) { lo[jj] = 0; hi[jj] = 0; }
-    const u64* ip = src + (((b * T) + sd.in0) << logN) + n;
-    double nu = 0.5;
-    u64 x = ip[0];
-    for (u32 i = 0; i < sd.sI; i++) {
-        u64 xn = (i + 1 < sd.sI) ? ip[(size_t)(i + 1) << logN] : 0ull;
-        nu = __dadd_rn(nu, __dmul_rn(sF[i], __ull2double_rn(x)));
+            for (int jj = 0; jj < JT; jj++) acc[jj].clear();
+            mac_towers<JT>(acc, sd.sI, reinterpret_cast<const uint4*>(sM), load, term);
+        } else {
 #pragma unroll
-        for (int jj = 0; jj < JT; jj++) mac128(lo[jj], hi[jj], x, sM[i * JT + jj]);
-        x = xn;
+            for (int jj = 0; jj < JT; jj++) { lo[jj] = 0; hi[jj] = 0; }
+            u64 x = ip[0];
+            for (u32 i = 0; i < sd.sI; i++) {
+                u64 xn = (i + 1 < sd.sI) ? ip[(size_t)(i + 1) << logN] : 0ull;
+                nu = __dadd_rn(nu, __dmul_rn(sF[i], __ull2double_rn(x)));
+#pragma unroll
+                for (int jj = 0; jj < JT; jj++) mac128(lo[jj], hi[jj], x, sM[i * JT + jj]);
+                x = xn;
+            }
+        }
+        // integer part of nu: utilities.h:133-137 decides between a 64-bit and a 128-bit conversion
+        u64 a_lo, a_hi = 0;
+        if (nu < 18446744073709551616.0) {
+            a_lo = __double2ull_rz(nu);
+        } else {
+            a_hi = __double2ull_rz(nu * 5.421010862427522e-20);                  // nu / 2^64: exact (power of two)
+            a_lo = __double2ull_rz(nu - __ull2double_rn(a_hi) * 18446744073709551616.0);
+        }
+#pragma unroll
+        for (int jj = 0; jj < JT; jj++) {
+            if (j0 + jj < sd.sO) {
+                const TargetMod tg = sT[jj];
+                u64 xo = src[(((b * T) + sd.out0 + j0 + jj) << logN) + n];
+                if constexpr (SPLIT) {                   // the output tower's own term: limbs are normalised, one more fits
+                    const uint4 h = reinterpret_cast<const uint4*>(sM)[sd.sI * JT + jj];
+                    u32 x0, x1;
+                    split30(xo, x0, x1);
+                    const u64 t0 = (u64)x0 * h.x, t2 = (u64)x1 * h.y, tm = (u64)(x0 + x1) * h.z;
+                    Acc30& A = acc[jj];
+                    A.a0 += t0; A.a1 += tm - t0 - t2; A.a2 += t2;
+                    A.normalise();
+                    A.value(lo[jj], hi[jj]);
+                } else {
+                    mac128(lo[jj], hi[jj], xo, sM[sd.sI * JT + jj]);
+                }
+                u64 r = reduce128(lo[jj], hi[jj], tg);
+                u64 a = reduce128(a_lo, a_hi, tg);
+                dst[(((b * sd.sO) + j0 + jj) << logN) + n] = addmod(r, a, tg.p);
+            }
+        }
     }
-    // integer part of nu: utilities.h:133-137 decides between a 64-bit and a 128-bit conversion
-    u64 a_lo, a_hi = 0;
-    if (nu < 18446744073709551616.0) {
-        a_lo = __double2ull_rz(nu);
-    } else {
-        a_hi = __double2ull_rz(nu * 5.421010862427522e-20);                  // nu / 2^64: exact (power of two)
-        a_lo = __double2ull_rz(nu - __ull2double_rn(a_hi) * 18446744073709551616.0);
-    }
-#pragma unroll
-    for (int jj = 0; jj < JT; jj++) {
-        if (j0 + jj < sd.sO) {
-            const BasisTarget tg = sd.tgt[j0 + jj];
-            u64 xo = src[(((b * T) + sd.out0 + j0 + jj) << logN) + n];
-            mac128(lo[jj], hi[jj], xo, sM[sd.sI * JT + jj]);
-            u64 r = barrett128(lo[jj], hi[jj], tg.p, tg.mu_lo, tg.mu_hi);
-            u64 a = barrett128(a_lo, a_hi, tg.p, tg.mu_lo, tg.mu_hi);
-            dst[(((b * sd.sO) + j0 + jj) << logN) + n] = addmod(r, a, tg.p);
+}
+
+template <int JT>
+static void launch_scale_round_jt(int jt, bool split, int nblk, size_t smem, cudaStream_t st, u64* d, const u64* s, size_t items,
+                                  u32 logN, const ScaleDev& sd) {
+    if constexpr (JT >= 1) {
+        if (jt == JT) {
+            const size_t tiles = (items + BS_THREADS - 1) / BS_THREADS;
+            if (split) {
+                auto k = scale_round_kernel<JT, true>;
+                k<<<dim3(persistent_grid_x(k, smem, tiles, nblk), nblk), BS_THREADS, smem, st>>>(d, s, items, logN, sd);
+            } else {
+                auto k = scale_round_kernel<(JT > 8 ? 8 : JT), false>;
+                k<<<dim3(persistent_grid_x(k, smem, tiles, nblk), nblk), BS_THREADS, smem, st>>>(d, s, items, logN, sd);
+            }
+        } else {
+            launch_scale_round_jt<JT - 1>(jt, split, nblk, smem, st, d, s, items, logN, sd);
         }
     }
 }
@@ -195,17 +417,12 @@ cudaError_t launch_scale_round(const ScaleDev& sd, uint64_t* dst, const uint64_t
                                cudaStream_t st) {
     size_t items = batch << logN;
     if (items == 0) return cudaSuccess;
-    int jt = sd.sO >= 8 ? 8 : sd.sO >= 4 ? 4 : sd.sO >= 2 ? 2 : 1;
-    dim3 grid((unsigned)((items + BS_THREADS - 1) / BS_THREADS), (sd.sO + jt - 1) / jt);
-    size_t smem = ((size_t)(sd.sI + 1) * jt + sd.sI) * 8;
-    u64* d = reinterpret_cast<u64*>(dst);
-    const u64* s = reinterpret_cast<const u64*>(src);
-    switch (jt) {
-        case 8: scale_round_kernel<8><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, sd); break;
-        case 4: scale_round_kernel<4><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, sd); break;
-        case 2: scale_round_kernel<2><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, sd); break;
-        default: scale_round_kernel<1><<<grid, BS_THREADS, smem, st>>>(d, s, items, logN, sd); break;
-    }
+    int jt, nblk;
+    column_blocks(sd.sO, sd.narrow != 0, jt, nblk);
+    nblk = (int)(sd.sO + jt - 1) / jt;
+    size_t smem = ((size_t)(sd.sI + 1) * jt * (sd.narrow ? 2 : 1) + sd.sI) * 8 + (size_t)jt * sizeof(TargetMod);
+    launch_scale_round_jt<BS_JT_MAX>(jt, sd.narrow != 0, nblk, smem, st, reinterpret_cast<u64*>(dst),
+                                     reinterpret_cast<const u64*>(src), items, logN, sd);
     kernel_launch_count_add(1);
     return cudaGetLastError();
 }

@@ -45,10 +45,18 @@ cudaError_t launch_automorphism_map(const RingDev& r, uint64_t* dst, const uint6
                                     const uint32_t* map, cudaStream_t st);
 // ---- RNS basis conversion (basis.cu) ----
 struct BasisTarget {             // one target modulus p_j of ApproxSwitchCRTBasis
-    uint64_t p, mu_lo, mu_hi;    // mu = floor(2^128 / p) (utils/utilities-int.h:60)
+    uint64_t p;
+    uint64_t c64, c64p;          // 2^64 mod p and its Shoup companion floor(c64 * 2^64 / p)   (128-bit sum -> residue, basis.cu)
+    uint64_t pinv;               // floor(2^64 / p)
     uint64_t post, postp;        // optional multiplier applied to the reduced value (0 = none) and its Shoup companion
-    uint64_t pad[3];
+    uint64_t pad[2];
 };
+inline void basis_target_set(BasisTarget& g, uint64_t p) {
+    g.p = p;
+    g.c64 = (uint64_t)((((unsigned __int128)1) << 64) % p);
+    g.c64p = (uint64_t)((((unsigned __int128)g.c64) << 64) / p);
+    g.pinv = (uint64_t)((((unsigned __int128)1) << 64) / p);
+}
 struct BasisDev {
     uint32_t sq, sp;
     const uint64_t* q;           // [sq] source moduli
@@ -57,12 +65,14 @@ struct BasisDev {
     const BasisTarget* tgt;      // [sp]
     const double* qinv;          // [sq] 1./double(q_i)                      (exact form only)
     const uint64_t* alphaq;      // [sq+1][sp] [alpha*Q]_{p_j}               (exact form only)
+    uint32_t narrow;             // 1: every q_i and every hat entry is below 2^60 -> carry-free 30-bit split accumulation
 };
 struct ScaleDev {                // DCRTPolyImpl::ScaleAndRound(paramsOutput, ...)
     uint32_t sI, sO, in0, out0;  // input / output tower counts and their first tower inside [sI+sO]
     const double* frac;          // [sI]
     const uint64_t* modo;        // [sO][sI+1]
-    const BasisTarget* tgt;      // [sO] output moduli with their 128-bit Barrett constants
+    const BasisTarget* tgt;      // [sO] output moduli with their reduction constants
+    uint32_t narrow;             // 1: input moduli and modo entries below 2^60 (see BasisDev::narrow)
 };
 // dst towers dst0.. of [batch][dstT][N] = ApproxSwitchCRTBasis of src towers src0..src0+sq-1 of [batch][srcT][N]
 cudaError_t launch_basis_switch(const BasisDev& bd, uint64_t* dst, uint32_t dstT, uint32_t dst0, const uint64_t* src,

@@ -811,6 +811,19 @@ uint64_t prod_mod(const std::vector<uint64_t>& f, size_t skip, uint64_t m) {   /
 }
 }  // namespace
 
+// The carry-free 30-bit split accumulation of basis.cu needs every factor below 2^60 (true of every modulus the reference
+// can produce, basicint.h:44-45); tables that are not take the 128-bit multiply-accumulate kernels instead.
+// FHE_B200_BASIS_WIDE=1 forces that form (tests run both).
+static bool all_below_2_60(const std::vector<uint64_t>& v) {
+    for (uint64_t x : v)
+        if (x >> 60) return false;
+    return true;
+}
+static bool basis_force_wide() {
+    const char* e = getenv("FHE_B200_BASIS_WIDE");
+    return e && *e && *e != '0';
+}
+
 struct fhe_basis {
     fhe_ctx* ctx = nullptr;
     fhe_ring *from = nullptr, *to = nullptr;
@@ -837,10 +850,7 @@ static void basis_fill(const fhe_basis* b, uint64_t t, std::vector<ulonglong2>& 
     }
     for (size_t j = 0; j < p.size(); j++) {
         BasisTarget g{};
-        g.p = p[j];
-        unsigned __int128 mu = (~(unsigned __int128)0) / p[j];              // floor(2^128 / p): p is not a power of two
-        g.mu_lo = (uint64_t)mu;
-        g.mu_hi = (uint64_t)(mu >> 64);
+        basis_target_set(g, p[j]);
         if (t) { g.post = t % p[j]; g.postp = host::shoup_companion(g.post, p[j]); }
         tgt[j] = g;
     }
@@ -900,6 +910,7 @@ extern "C" int fhe_basis_create(fhe_ring* from, fhe_ring* to, const uint64_t* qh
     b->dev.pre = (const ulonglong2*)b->d_pre;
     b->dev.hat = (const uint64_t*)b->d_hat;
     b->dev.tgt = (const BasisTarget*)b->d_tgt;
+    b->dev.narrow = !basis_force_wide() && all_below_2_60(from->q) && all_below_2_60(b->hat_modp);
     *out = b;
     return FHE_OK;
 }
@@ -1239,8 +1250,7 @@ extern "C" int fhe_scale_round_create(fhe_ring* ring, uint32_t size_out, int out
         BasisTarget g{};
         g.p = ring->q[out0 + j];
         if ((g.p & (g.p - 1)) == 0) { delete p; return fail(FHE_EINVAL, "fhe_scale_round_create: output modulus is a power of two"); }
-        unsigned __int128 mu = (~(unsigned __int128)0) / g.p;
-        g.mu_lo = (uint64_t)mu; g.mu_hi = (uint64_t)(mu >> 64);
+        basis_target_set(g, g.p);
         tgt[j] = g;
     }
     int rc;
@@ -1252,6 +1262,7 @@ extern "C" int fhe_scale_round_create(fhe_ring* ring, uint32_t size_out, int out
     p->dev.frac = (const double*)p->d_frac;
     p->dev.modo = (const uint64_t*)p->d_modo;
     p->dev.tgt = (const BasisTarget*)p->d_tgt;
+    p->dev.narrow = !basis_force_wide() && all_below_2_60(ring->q) && all_below_2_60(m);
     *out = p;
     return FHE_OK;
 }
