@@ -33,10 +33,13 @@ cudaError_t launch_vec(int op, uint64_t* dst, const uint64_t* a, const uint64_t*
 // dst[i] = a[i] (op) s mod q
 cudaError_t launch_vec_scalar(int op, uint64_t* dst, const uint64_t* a, uint64_t s, size_t n,
                               uint64_t q, cudaStream_t st);
-// In-place forward / inverse negacyclic NTT of every tower of every batch item.
+// Forward / inverse negacyclic NTT of every tower of every batch item, result in data.
 // algo: 0 = auto, 1 = force the single-CTA shared-memory kernel (N <= 4096).
+// src: buffer the transform reads (nullptr = data, in place).  outT / inT: towers per batch item in the memory of data /
+// src (0 = r.T): the r.T towers transformed are the first ones of each item, so a pointer offset by t0 * N transforms
+// towers t0 .. t0 + r.T - 1 of a wider poly in place.
 cudaError_t launch_ntt(const RingDev& r, uint64_t* data, size_t batch, bool inverse,
-                       cudaStream_t st, int algo);
+                       cudaStream_t st, int algo, const uint64_t* src = nullptr, uint32_t outT = 0, uint32_t inT = 0);
 // dst = automorphism X -> X^k of src over [batch][T][N] (k odd, dst != src).  format 0 EVALUATION, 1 COEFFICIENT.
 cudaError_t launch_automorphism(const RingDev& r, uint64_t* dst, const uint64_t* src, size_t batch, uint32_t k,
                                 int format, cudaStream_t st);

@@ -206,9 +206,9 @@ struct StridedCfg {
 
 template <int RL, int TL, bool INV>
 __global__ void __launch_bounds__(StridedCfg<RL, TL>::THREADS)
-ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
+ntt_strided_kernel(u64* __restrict__ data, const u64* __restrict__ in, const ulonglong2* __restrict__ twAll,
                    const TowerMod* __restrict__ mods, const ulonglong2* __restrict__ invc,
-                   u32 T, u32 logN) {
+                   u32 T, u32 logN, u32 outT, u32 inT) {
     using K = StridedCfg<RL, TL>;
     auto sidx = [](u32 row, u32 c) -> u32 { return row * K::C + c + (row >> K::B) * K::PAD; };
     extern __shared__ __align__(16) u64 sm[];
@@ -220,7 +220,11 @@ ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
     const u64 q = mods[tower].q, nq = 0ull - q;
     const QMul Q = make_qmul(q);
     const ulonglong2* tw = twAll + ((size_t)tower << logN);
-    u64* base = data + ((size_t)unit << logN) + cg * C;
+    // towers of one batch item sit outT (inT) towers apart in memory: a view of a wider poly transforms in place,
+    // and the first pass of a transform may read another buffer (in) than the one it leaves its result in (data)
+    const u32 bitem = unit / T;
+    u64* base = data + (((size_t)bitem * outT + tower) << logN) + cg * C;
+    const u64* ibase = in + (((size_t)bitem * inT + tower) << logN) + cg * C;
     const u32 tid = threadIdx.x;
 
     if (!INV) {
@@ -231,7 +235,7 @@ ntt_strided_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
             u32 c = item % C, ulow = item / C;
             u64 x[1 << A];
 #pragma unroll
-            for (int e = 0; e < (1 << A); e++) x[e] = base[((size_t)((e << B) + ulow) << 8) + c];
+            for (int e = 0; e < (1 << A); e++) x[e] = ibase[((size_t)((e << B) + ulow) << 8) + c];
             fwd_step<A, 1>(x, tw, 1u, Q, nq);
             if (B == 0) {
 #pragma unroll
@@ -309,8 +313,8 @@ struct ContigCfg {
 
 template <int LB, bool INV>
 __global__ void __launch_bounds__(ContigCfg<LB>::THREADS)
-ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
-                  const TowerMod* __restrict__ mods, u32 T, u32 logN, u32 batch, u32 logCB) {
+ntt_contig_kernel(u64* __restrict__ data, const u64* __restrict__ in, const ulonglong2* __restrict__ twAll,
+                  const TowerMod* __restrict__ mods, u32 T, u32 logN, u32 batch, u32 logCB, u32 outT, u32 inT) {
     using K = ContigCfg<LB>;
     constexpr u32 NC = K::NC, TH = K::THREADS;
     extern __shared__ __align__(16) u64 sm[];
@@ -334,7 +338,11 @@ ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
         u32 b = bg * CB + (c & (CB - 1));
         h = hg * CH + (c >> logCB);
         ok = b < batch;
-        return data + (((size_t)b * T + tower) << logN) + ((size_t)h << 8);
+        return data + (((size_t)b * outT + tower) << logN) + ((size_t)h << 8);
+    };
+    auto in_ptr = [&](u32 c) -> const u64* {         // the same block in the buffer the inverse transform reads
+        u32 b = bg * CB + (c & (CB - 1));
+        return in + (((size_t)b * inT + tower) << logN) + ((size_t)(hg * CH + (c >> logCB)) << 8);
     };
 
     if (!INV) {
@@ -374,7 +382,8 @@ ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
 #pragma unroll
         for (u32 k = 0; k < NC; k++) {
             u32 h; bool ok;
-            u64* p = blk_ptr(k, ok, h);
+            (void)blk_ptr(k, ok, h);
+            const u64* p = in_ptr(k);
 #pragma unroll
             for (u32 u = tid; u < 256; u += TH) sm[K::idx(u, k)] = ok ? p[u] : 0ull;
         }
@@ -411,16 +420,17 @@ ntt_contig_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
 // ------------------------------------------------------------------------------------------
 template <bool INV>
 __global__ void __launch_bounds__(256)
-ntt_small_kernel(u64* __restrict__ data, const ulonglong2* __restrict__ twAll,
+ntt_small_kernel(u64* __restrict__ data, const u64* __restrict__ in, const ulonglong2* __restrict__ twAll,
                  const TowerMod* __restrict__ mods, const ulonglong2* __restrict__ invc,
-                 u32 T, u32 logN) {
+                 u32 T, u32 logN, u32 outT, u32 inT) {
     extern __shared__ __align__(16) u64 sm[];
     const u32 N = 1u << logN;
     const u32 unit = blockIdx.x, tower = unit % T;
     const u64 q = mods[tower].q;
     const ulonglong2* tw = twAll + ((size_t)tower << logN);
-    u64* p = data + ((size_t)unit << logN);
-    for (u32 i = threadIdx.x; i < N; i += blockDim.x) sm[i] = p[i];
+    u64* p = data + (((size_t)(unit / T) * outT + tower) << logN);
+    const u64* pi = in + (((size_t)(unit / T) * inT + tower) << logN);
+    for (u32 i = threadIdx.x; i < N; i += blockDim.x) sm[i] = pi[i];
     __syncthreads();
     if (!INV) {
         for (u32 s = 0; s < logN; s++) {              // m = 2^s, t = N >> (s+1)
@@ -469,7 +479,7 @@ static int tile_log(int which) {
 }
 
 template <int RL, int TL, bool INV>
-static cudaError_t launch_strided_t(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
+static cudaError_t launch_strided_t(const RingDev& r, u64* data, const u64* in, u32 outT, u32 inT, size_t batch, cudaStream_t st) {
     using K = StridedCfg<RL, TL>;
     static bool attr_done = false;
     if (!attr_done && K::SMEM > 48 * 1024) {
@@ -480,40 +490,40 @@ static cudaError_t launch_strided_t(const RingDev& r, u64* data, size_t batch, c
     }
     size_t grid = batch * r.T * (256 / K::C);
     ntt_strided_kernel<RL, TL, INV><<<(unsigned)grid, K::THREADS, K::SMEM, st>>>(
-        data, INV ? r.twI : r.twF, r.mods, r.invc, r.T, r.logN);
+        data, in, INV ? r.twI : r.twF, r.mods, r.invc, r.T, r.logN, outT, inT);
     kernel_launch_count_add(1);
     return cudaGetLastError();
 }
 
 template <int RL, bool INV>
-static cudaError_t launch_strided_rl(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
+static cudaError_t launch_strided_rl(const RingDev& r, u64* data, const u64* in, u32 outT, u32 inT, size_t batch, cudaStream_t st) {
     if constexpr (RL >= 4) {                       // smaller rings: the tile is already below 4096 coefficients
         switch (tile_log(0)) {
-            case 9:  if constexpr (RL >= 7) return launch_strided_t<RL, 9, INV>(r, data, batch, st);
-            case 10: if constexpr (RL >= 6) return launch_strided_t<RL, 10, INV>(r, data, batch, st);
-            case 11: if constexpr (RL >= 5) return launch_strided_t<RL, 11, INV>(r, data, batch, st);
+            case 9:  if constexpr (RL >= 7) return launch_strided_t<RL, 9, INV>(r, data, in, outT, inT, batch, st);
+            case 10: if constexpr (RL >= 6) return launch_strided_t<RL, 10, INV>(r, data, in, outT, inT, batch, st);
+            case 11: if constexpr (RL >= 5) return launch_strided_t<RL, 11, INV>(r, data, in, outT, inT, batch, st);
         }
     }
-    return launch_strided_t<RL, 12, INV>(r, data, batch, st);
+    return launch_strided_t<RL, 12, INV>(r, data, in, outT, inT, batch, st);
 }
 
 template <bool INV>
-static cudaError_t launch_strided(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
+static cudaError_t launch_strided(const RingDev& r, u64* data, const u64* in, u32 outT, u32 inT, size_t batch, cudaStream_t st) {
     switch (r.logN - 8) {
-        case 1: return launch_strided_rl<1, INV>(r, data, batch, st);
-        case 2: return launch_strided_rl<2, INV>(r, data, batch, st);
-        case 3: return launch_strided_rl<3, INV>(r, data, batch, st);
-        case 4: return launch_strided_rl<4, INV>(r, data, batch, st);
-        case 5: return launch_strided_rl<5, INV>(r, data, batch, st);
-        case 6: return launch_strided_rl<6, INV>(r, data, batch, st);
-        case 7: return launch_strided_rl<7, INV>(r, data, batch, st);
-        case 8: return launch_strided_rl<8, INV>(r, data, batch, st);
+        case 1: return launch_strided_rl<1, INV>(r, data, in, outT, inT, batch, st);
+        case 2: return launch_strided_rl<2, INV>(r, data, in, outT, inT, batch, st);
+        case 3: return launch_strided_rl<3, INV>(r, data, in, outT, inT, batch, st);
+        case 4: return launch_strided_rl<4, INV>(r, data, in, outT, inT, batch, st);
+        case 5: return launch_strided_rl<5, INV>(r, data, in, outT, inT, batch, st);
+        case 6: return launch_strided_rl<6, INV>(r, data, in, outT, inT, batch, st);
+        case 7: return launch_strided_rl<7, INV>(r, data, in, outT, inT, batch, st);
+        case 8: return launch_strided_rl<8, INV>(r, data, in, outT, inT, batch, st);
     }
     return cudaErrorInvalidValue;
 }
 
 template <int LB, bool INV>
-static cudaError_t launch_contig_t(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
+static cudaError_t launch_contig_t(const RingDev& r, u64* data, const u64* in, u32 outT, u32 inT, size_t batch, cudaStream_t st) {
     using K = ContigCfg<LB>;
     const u32 N1 = r.N >> 8, NC = K::NC;
     u32 logCB = 0;                                   // batch items per tile: largest 2^k <= min(batch, NC) ...
@@ -521,49 +531,52 @@ static cudaError_t launch_contig_t(const RingDev& r, u64* data, size_t batch, cu
     while ((NC >> logCB) > N1) logCB++;              // ... but never more blocks per tile than the ring has
     const u32 CB = 1u << logCB, CH = NC >> logCB;
     size_t grid = (size_t)r.T * ((batch + CB - 1) / CB) * (N1 / CH);
-    ntt_contig_kernel<LB, INV><<<(unsigned)grid, K::THREADS, K::SMEM + 128, st>>>(data, INV ? r.twI : r.twF, r.mods,
-                                                                          r.T, r.logN, (u32)batch, logCB);
+    ntt_contig_kernel<LB, INV><<<(unsigned)grid, K::THREADS, K::SMEM + 128, st>>>(data, in, INV ? r.twI : r.twF, r.mods,
+                                                                          r.T, r.logN, (u32)batch, logCB, outT, inT);
     kernel_launch_count_add(1);
     return cudaGetLastError();
 }
 
 template <bool INV>
-static cudaError_t launch_contig(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
+static cudaError_t launch_contig(const RingDev& r, u64* data, const u64* in, u32 outT, u32 inT, size_t batch, cudaStream_t st) {
     const u32 N1 = r.N >> 8;
     switch (tile_log(1)) {
-        case 9:  return launch_contig_t<1, INV>(r, data, batch, st);
-        case 10: if (N1 >= 4 || batch >= 4) return launch_contig_t<2, INV>(r, data, batch, st);
-        case 11: if (N1 >= 8 || batch >= 8) return launch_contig_t<3, INV>(r, data, batch, st);
+        case 9:  return launch_contig_t<1, INV>(r, data, in, outT, inT, batch, st);
+        case 10: if (N1 >= 4 || batch >= 4) return launch_contig_t<2, INV>(r, data, in, outT, inT, batch, st);
+        case 11: if (N1 >= 8 || batch >= 8) return launch_contig_t<3, INV>(r, data, in, outT, inT, batch, st);
     }
-    return launch_contig_t<4, INV>(r, data, batch, st);
+    return launch_contig_t<4, INV>(r, data, in, outT, inT, batch, st);
 }
 
 template <bool INV>
-static cudaError_t launch_small(const RingDev& r, u64* data, size_t batch, cudaStream_t st) {
+static cudaError_t launch_small(const RingDev& r, u64* data, const u64* in, u32 outT, u32 inT, size_t batch, cudaStream_t st) {
     size_t smem = (size_t)r.N * 8;
-    ntt_small_kernel<INV><<<(unsigned)(batch * r.T), 256, smem, st>>>(data, INV ? r.twI : r.twF,
-                                                                     r.mods, r.invc, r.T, r.logN);
+    ntt_small_kernel<INV><<<(unsigned)(batch * r.T), 256, smem, st>>>(data, in, INV ? r.twI : r.twF,
+                                                                     r.mods, r.invc, r.T, r.logN, outT, inT);
     kernel_launch_count_add(1);
     return cudaGetLastError();
 }
 
 cudaError_t launch_ntt(const RingDev& r, uint64_t* data, size_t batch, bool inverse,
-                       cudaStream_t st, int algo) {
+                       cudaStream_t st, int algo, const uint64_t* src, uint32_t outT, uint32_t inT) {
     if (batch == 0) return cudaSuccess;
     if (batch * r.T * 16 > 0x7fffffffull) return cudaErrorInvalidValue;   // grid.x limit
     u64* d = reinterpret_cast<u64*>(data);
+    const u64* in = src ? reinterpret_cast<const u64*>(src) : d;         // the first pass reads src, everything else is in place
+    if (!outT) outT = r.T;
+    if (!inT) inT = src ? r.T : outT;
     if (r.logN <= 8 || (algo == 1 && r.logN <= 12))
-        return inverse ? launch_small<true>(r, d, batch, st) : launch_small<false>(r, d, batch, st);
+        return inverse ? launch_small<true>(r, d, in, outT, inT, batch, st) : launch_small<false>(r, d, in, outT, inT, batch, st);
     if (r.logN > 16) return cudaErrorInvalidValue;
     cudaError_t e;
     if (!inverse) {
-        e = launch_strided<false>(r, d, batch, st);
+        e = launch_strided<false>(r, d, in, outT, inT, batch, st);
         if (e != cudaSuccess) return e;
-        return launch_contig<false>(r, d, batch, st);
+        return launch_contig<false>(r, d, d, outT, outT, batch, st);
     }
-    e = launch_contig<true>(r, d, batch, st);
+    e = launch_contig<true>(r, d, in, outT, inT, batch, st);
     if (e != cudaSuccess) return e;
-    return launch_strided<true>(r, d, batch, st);
+    return launch_strided<true>(r, d, d, outT, outT, batch, st);
 }
 
 }  // namespace fhe

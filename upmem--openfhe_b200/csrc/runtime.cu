@@ -941,10 +941,22 @@ static cudaError_t copy_towers(uint64_t* dst, uint32_t dT, uint32_t d0, const ui
                              (size_t)cnt * N * 8, batch, cudaMemcpyDeviceToDevice, s);
 }
 
-static int ring_ntt(fhe_ring* r, uint64_t* x, size_t batch, bool inverse, cudaStream_t s, const char* who) {
-    if (r->ntt_identity || r->dev.N == 1) return FHE_OK;
+// NTT of the r->T towers that start at x (outT towers apart per batch item; 0 = packed).  With src the transform reads
+// there (inT towers apart) and leaves src untouched: no staging copy, and a result can be produced straight into its
+// towers of a wider poly.
+static int ring_ntt(fhe_ring* r, uint64_t* x, size_t batch, bool inverse, cudaStream_t s, const char* who,
+                    const uint64_t* src = nullptr, uint32_t outT = 0, uint32_t inT = 0) {
+    const uint32_t T = r->dev.T, N = r->dev.N;
+    if (!outT) outT = T;
+    if (!inT) inT = src ? T : outT;
+    if (r->ntt_identity || N == 1) {
+        if (src && src != x)
+            CUDA_TRY(cudaMemcpy2DAsync(x, (size_t)outT * N * 8, src, (size_t)inT * N * 8, (size_t)T * N * 8, batch,
+                                       cudaMemcpyDeviceToDevice, s));
+        return FHE_OK;
+    }
     if (!r->has_ntt) return fail(FHE_EINVAL, "%s: a ring was created without roots of unity", who);
-    CUDA_TRY(launch_ntt(r->dev, x, batch, inverse, s, 0));
+    CUDA_TRY(launch_ntt(r->dev, x, batch, inverse, s, 0, src, outT, inT));
     return FHE_OK;
 }
 
@@ -959,21 +971,21 @@ extern "C" int fhe_approx_mod_up(fhe_basis* b, fhe_dptr dst_qp, fhe_dptr src_q, 
     const uint32_t N = b->from->dev.N, logN = b->from->dev.logN, sq = b->dev.sq, sp = b->dev.sp;
     uint64_t* dst = (uint64_t*)(uintptr_t)dst_qp;
     const uint64_t* src = (const uint64_t*)(uintptr_t)src_q;
-    const size_t wq = batch * sq * (size_t)N, wp = batch * sp * (size_t)N;
-    if ((rc = b->s0.need(b->ctx, wq * 8)) || (rc = b->s1.need(b->ctx, wp * 8))) return rc;
-    uint64_t* coef = (uint64_t*)b->s0.p;
-    uint64_t* partP = (uint64_t*)b->s1.p;
-    // COEFFICIENT form of the Q towers (dcrtpoly-impl.h:1096-1099)
-    CUDA_TRY(cudaMemcpyAsync(coef, src, wq * 8, cudaMemcpyDeviceToDevice, s));
-    if (format == 0 && (rc = ring_ntt(b->from, coef, batch, true, s, "fhe_approx_mod_up"))) return rc;
-    CUDA_TRY(launch_basis_switch(b->dev, partP, sp, 0, coef, sq, 0, batch, logN, false, s));          // :1105-1106
-    if ((rc = ring_ntt(b->to, partP, batch, false, s, "fhe_approx_mod_up"))) return rc;        // :1113-1116
-    CUDA_TRY(copy_towers(dst, sq + sp, sq, partP, sp, 0, sp, batch, N, s));
+    const size_t wq = batch * sq * (size_t)N;
+    const char* who = "fhe_approx_mod_up";
+    const uint64_t* coef = src;                              // COEFFICIENT form of the Q towers (dcrtpoly-impl.h:1096-1099)
+    if (format == 0) {
+        if ((rc = b->s0.need(b->ctx, wq * 8))) return rc;
+        if ((rc = ring_ntt(b->from, (uint64_t*)b->s0.p, batch, true, s, who, src))) return rc;
+        coef = (const uint64_t*)b->s0.p;
+    }
+    // the P towers are produced where they belong in dst and transformed there (:1105-1106, :1113-1116)
+    CUDA_TRY(launch_basis_switch(b->dev, dst, sq + sp, sq, coef, sq, 0, batch, logN, false, s));
+    if ((rc = ring_ntt(b->to, dst + (size_t)sq * N, batch, false, s, who, nullptr, sq + sp))) return rc;
     if (format == 0) {
         CUDA_TRY(copy_towers(dst, sq + sp, 0, src, sq, 0, sq, batch, N, s));                   // :1119-1123
     } else {
-        if ((rc = ring_ntt(b->from, coef, batch, false, s, "fhe_approx_mod_up"))) return rc;   // :1124-1130
-        CUDA_TRY(copy_towers(dst, sq + sp, 0, coef, sq, 0, sq, batch, N, s));
+        if ((rc = ring_ntt(b->from, dst, batch, false, s, who, src, sq + sp, sq))) return rc;  // :1124-1130
     }
     return FHE_OK;
 }
@@ -1019,8 +1031,7 @@ extern "C" int fhe_approx_mod_down(fhe_basis* b, fhe_dptr dst_q, fhe_dptr src_qp
     if ((rc = b->s0.need(b->ctx, wp * 8)) || (rc = b->s1.need(b->ctx, wq * 8))) return rc;
     uint64_t* partP = (uint64_t*)b->s0.p;
     uint64_t* sw = (uint64_t*)b->s1.p;
-    CUDA_TRY(copy_towers(partP, sp, 0, src, sq + sp, sq, sp, batch, N, s));                    // :1150-1151
-    if ((rc = ring_ntt(P, partP, batch, true, s, "fhe_approx_mod_down"))) return rc;
+    if ((rc = ring_ntt(P, partP, batch, true, s, "fhe_approx_mod_down", src + (size_t)sq * N, sp, sq + sp))) return rc;   // :1150-1151
     CUDA_TRY(launch_basis_switch(bd, sw, sq, 0, partP, sp, 0, batch, logN, false, s));                // :1152-1159, :1170-1171
     if ((rc = ring_ntt(Q, sw, batch, false, s, "fhe_approx_mod_down"))) return rc;             // :1172
     CUDA_TRY(launch_tower_affine(0, dst, src, sw, batch, logN, sq, sq + sp, Q->dev.mods,       // :1173
@@ -1133,8 +1144,11 @@ static int rescale_run(fhe_rescale* p, fhe_dptr dst_, fhe_dptr src_, size_t batc
     if ((rc = p->s0.need(p->ctx, batch * (size_t)N * 8)) || (rc = p->s1.need(p->ctx, batch * l * (size_t)N * 8))) return rc;
     uint64_t* lastp = (uint64_t*)p->s0.p;
     uint64_t* tmp = (uint64_t*)p->s1.p;
-    CUDA_TRY(copy_towers(lastp, 1, 0, src, T, l, 1, batch, N, s));
-    if (format == 0 && (rc = ring_ntt(p->last, lastp, batch, true, s, who))) return rc;        // SetFormat(COEFFICIENT)
+    if (format == 0) {                                                                         // SetFormat(COEFFICIENT)
+        if ((rc = ring_ntt(p->last, lastp, batch, true, s, who, src + (size_t)l * N, 1, T))) return rc;
+    } else {
+        CUDA_TRY(copy_towers(lastp, 1, 0, src, T, l, 1, batch, N, s));
+    }
     CUDA_TRY(launch_rescale_spread(tmp, lastp, batch, logN, l, ql, (const ulonglong4*)p->d_sw, kspread, p->pre_t, t ? 1 : 0, s));
     if (format == 0 && (rc = ring_ntt(p->rest, tmp, batch, false, s, who))) return rc;
     CUDA_TRY(launch_tower_affine(t ? 2 : 1, dst, src, tmp, batch, logN, l, T, p->rest->dev.mods, ktail, s));
@@ -1196,20 +1210,21 @@ extern "C" int fhe_expand_crt_basis(fhe_basis* b, fhe_dptr dst_qp, fhe_dptr src_
     const uint32_t N = b->from->dev.N, logN = b->from->dev.logN, sq = b->dev.sq, sp = b->dev.sp;
     uint64_t* dst = (uint64_t*)(uintptr_t)dst_qp;
     const uint64_t* src = (const uint64_t*)(uintptr_t)src_q;
-    const size_t wq = batch * sq * (size_t)N, wp = batch * sp * (size_t)N;
-    if ((rc = b->s0.need(b->ctx, wq * 8)) || (rc = b->s1.need(b->ctx, wp * 8))) return rc;
-    uint64_t* coef = (uint64_t*)b->s0.p;
-    uint64_t* partP = (uint64_t*)b->s1.p;
+    const size_t wq = batch * sq * (size_t)N;
     const char* who = "fhe_expand_crt_basis";
-    CUDA_TRY(cudaMemcpyAsync(coef, src, wq * 8, cudaMemcpyDeviceToDevice, s));
-    if (format == 0 && (rc = ring_ntt(b->from, coef, batch, true, s, who))) return rc;         // dcrtpoly-impl.h:1321-1324
-    CUDA_TRY(launch_basis_switch(b->dev, partP, sp, 0, coef, sq, 0, batch, logN, true, s));    // :1326-1327
-    if (result_format == 0 && (rc = ring_ntt(b->to, partP, batch, false, s, who))) return rc;  // :1338-1341
-    CUDA_TRY(copy_towers(dst, sq + sp, sq, partP, sp, 0, sp, batch, N, s));
+    const uint64_t* coef = src;
+    if (format == 0) {                                                                         // dcrtpoly-impl.h:1321-1324
+        if ((rc = b->s0.need(b->ctx, wq * 8))) return rc;
+        if ((rc = ring_ntt(b->from, (uint64_t*)b->s0.p, batch, true, s, who, src))) return rc;
+        coef = (const uint64_t*)b->s0.p;
+    }
+    CUDA_TRY(launch_basis_switch(b->dev, dst, sq + sp, sq, coef, sq, 0, batch, logN, true, s));          // :1326-1327
+    if (result_format == 0 && (rc = ring_ntt(b->to, dst + (size_t)sq * N, batch, false, s, who, nullptr, sq + sp))) return rc;  // :1338-1341
     if (result_format == 0 && format == 0) {
         CUDA_TRY(copy_towers(dst, sq + sp, 0, src, sq, 0, sq, batch, N, s));                   // :1346-1349
+    } else if (result_format == 0) {
+        if ((rc = ring_ntt(b->from, dst, batch, false, s, who, src, sq + sp, sq))) return rc;  // :1350-1355
     } else {
-        if (result_format == 0 && (rc = ring_ntt(b->from, coef, batch, false, s, who))) return rc;   // :1350-1355
         CUDA_TRY(copy_towers(dst, sq + sp, 0, coef, sq, 0, sq, batch, N, s));                  // COEFFICIENT result keeps coef
     }
     return FHE_OK;
