@@ -483,6 +483,11 @@ def ntt_extra(pkg, be):
         out["approx_switch_crt_basis_n65536_q30_p10_b16"] = {
             "ms": ms, "mac128_per_s": batch * n * sq * sp / (ms * 1e-3), "polys_per_s": batch / (ms * 1e-3),
             "note": "one 64x64->128 multiply-accumulate per (source tower, target tower, coefficient)"}
+        ms = timed(lambda: p2q.approx_switch(dq, dp, batch))
+        out["approx_switch_crt_basis_n65536_q10_p30_b16"] = {
+            "ms": ms, "mac128_per_s": batch * n * sq * sp / (ms * 1e-3), "polys_per_s": batch / (ms * 1e-3),
+            "note": "the key-switching shape: few source towers, many target towers"}
+        rq.fill_uniform(dq, batch, 20260030)
         ms = timed(lambda: q2p.approx_mod_up(dr, dq, batch, 0))
         out["approx_mod_up_n65536_q30_p10_b16"] = {"ms": ms, "polys_per_s": batch / (ms * 1e-3)}
         ms = timed(lambda: p2q.approx_mod_down(dq, dqp, batch, 0))

@@ -213,18 +213,21 @@ ntt_strided_kernel(u64* __restrict__ data, const u64* __restrict__ in, const ulo
     auto sidx = [](u32 row, u32 c) -> u32 { return row * K::C + c + (row >> K::B) * K::PAD; };
     extern __shared__ __align__(16) u64 sm[];
     constexpr int A = K::A, B = K::B, C = K::C;
-    const u32 tilesPerUnit = 256 / C;
-    const u32 unit  = blockIdx.x / tilesPerUnit;
+    constexpr u32 tilesPerUnit = 256 / C;
+    const u32 tower = blockIdx.x / tilesPerUnit;      // grid: x = (tower, column group), y/z = batch item
     const u32 cg    = blockIdx.x % tilesPerUnit;
-    const u32 tower = unit % T;
     const u64 q = mods[tower].q, nq = 0ull - q;
     const QMul Q = make_qmul(q);
     const ulonglong2* tw = twAll + ((size_t)tower << logN);
     // towers of one batch item sit outT (inT) towers apart in memory: a view of a wider poly transforms in place,
     // and the first pass of a transform may read another buffer (in) than the one it leaves its result in (data)
-    const u32 bitem = unit / T;
+    const u32 bitem = blockIdx.z * gridDim.y + blockIdx.y;
     u64* base = data + (((size_t)bitem * outT + tower) << logN) + cg * C;
+#ifdef FHE_NTT_INPLACE_ONLY
+    const u64* ibase = base;
+#else
     const u64* ibase = in + (((size_t)bitem * inT + tower) << logN) + cg * C;
+#endif
     const u32 tid = threadIdx.x;
 
     if (!INV) {
@@ -342,6 +345,9 @@ ntt_contig_kernel(u64* __restrict__ data, const u64* __restrict__ in, const ulon
     };
     auto in_ptr = [&](u32 c) -> const u64* {         // the same block in the buffer the inverse transform reads
         u32 b = bg * CB + (c & (CB - 1));
+#ifdef FHE_NTT_INPLACE_ONLY
+        return data + (((size_t)b * outT + tower) << logN) + ((size_t)(hg * CH + (c >> logCB)) << 8);
+#endif
         return in + (((size_t)b * inT + tower) << logN) + ((size_t)(hg * CH + (c >> logCB)) << 8);
     };
 
@@ -488,8 +494,16 @@ static cudaError_t launch_strided_t(const RingDev& r, u64* data, const u64* in, 
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    size_t grid = batch * r.T * (256 / K::C);
-    ntt_strided_kernel<RL, TL, INV><<<(unsigned)grid, K::THREADS, K::SMEM, st>>>(
+    // batch items along y (and z beyond 32768 of them: the largest divisor of the batch that fits)
+    unsigned by = (unsigned)batch, bz = 1;
+    while (by > 32768u) {
+        unsigned d = 2;
+        while (by % d) d++;
+        by /= d; bz *= d;
+    }
+    if (bz > 65535u) return cudaErrorInvalidValue;
+    dim3 grid(r.T * (256 / K::C), by, bz);
+    ntt_strided_kernel<RL, TL, INV><<<grid, K::THREADS, K::SMEM, st>>>(
         data, in, INV ? r.twI : r.twF, r.mods, r.invc, r.T, r.logN, outT, inT);
     kernel_launch_count_add(1);
     return cudaGetLastError();
