@@ -202,6 +202,31 @@ int fhe_switch_crt_basis(fhe_basis* basis, fhe_dptr dst, fhe_dptr src, size_t ba
 int fhe_expand_crt_basis(fhe_basis* q_to_p, fhe_dptr dst_qp, fhe_dptr src_q, size_t batch, int format, int result_format,
                          int stream);
 
+/* DCRTPolyImpl::ExpandCRTBasisReverseOrder (dcrtpoly-impl.h:1361-1410, the multiparty key-switching form): as
+ * fhe_expand_crt_basis, but the new towers come first: dst over PQ [batch][sp+sq][N]. */
+int fhe_expand_crt_basis_reverse_order(fhe_basis* q_to_p, fhe_dptr dst_pq, fhe_dptr src_q, size_t batch, int format,
+                                       int result_format, int stream);
+/* DCRTPolyImpl::FastExpandCRTBasisPloverQ (dcrtpoly-impl.h:1413-1468; BFV multTech HPSPOVERQ / HPSPOVERQLEVELED):
+ * src over Q -> dst over QlPl [batch][sql+spl][N] holding x*Pl/Q.  q_to_pl is created with the scheme's tables
+ * qhat_inv_modq = m_negRlQHatInvModq[l] ([-Pl*(Q/q_i)^-1]_{q_i}) and qhat_modp = m_qInvModr ([q_i^-1]_{p_j})
+ * (bfvrns-cryptoparameters.cpp:501-523); pl_to_ql is the exact switch Pl -> Ql with its tables derived from the moduli
+ * (m_RlHatInvModr, m_RlHatModq, m_alphaRlModq, m_rInv: :390-443).  No NTT: the format is whatever src is in (the scheme
+ * calls it in COEFFICIENT).  src is not modified. */
+int fhe_fast_expand_crt_basis_pl_over_q(fhe_basis* q_to_pl, fhe_basis* pl_to_ql, fhe_dptr dst_qlpl, fhe_dptr src_q,
+                                        size_t batch, int stream);
+
+typedef struct fhe_tower_scale fhe_tower_scale;  /* one constant c_i < q_i per tower of `ring` (+ Shoup companions) */
+int fhe_tower_scale_create(fhe_ring* ring, const uint64_t* c, fhe_tower_scale** out);
+int fhe_tower_scale_destroy(fhe_tower_scale* plan);
+/* DCRTPolyImpl::ExpandCRTBasisQlHat (dcrtpoly-impl.h:1514-1534) with c = m_QlHatModq[l] over the ring Q: src over the
+ * first size_ql towers [batch][size_ql][N] -> dst over Q [batch][T][N]: towers < size_ql multiplied by c_i, the rest
+ * zero.  Format preserved. */
+int fhe_expand_crt_basis_ql_hat(fhe_tower_scale* plan, uint32_t size_ql, fhe_dptr dst_q, fhe_dptr src_ql, size_t batch,
+                                int stream);
+/* DCRTPolyImpl::ScaleAndRoundPOverQ (dcrtpoly-impl.h:2052-2066) with c = pInvModq over the ring Q (T towers): src over
+ * Q plus one extra tower p [batch][T+1][N] -> dst over Q: ((x_i - (x_p mod q_i)) mod q_i) * c_i.  Format preserved. */
+int fhe_scale_and_round_p_over_q(fhe_tower_scale* plan, fhe_dptr dst_q, fhe_dptr src_qp, size_t batch, int stream);
+
 typedef struct fhe_scale_round fhe_scale_round;
 /* DCRTPolyImpl::ScaleAndRound(paramsOutput, tOSHatInvModsDivsModo, tOSHatInvModsDivsFrac, modoBarretMu)
  * (dcrtpoly-impl.h:1876-1960): `ring` = the input basis (sI + size_out towers); the output moduli are its last

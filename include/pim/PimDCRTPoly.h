@@ -147,6 +147,25 @@ private:
   fhe_scale_round *plan_ = nullptr;
 };
 
+/* One constant per tower: m_QlHatModq[l] for ExpandCRTBasisQlHat, pInvModq for ScaleAndRoundPOverQ
+ * (dcrtpoly-impl.h:1514-1534, 2052-2066; BFV multTech HPSPOVERQ / HPSPOVERQLEVELED). */
+class PimTowerScale {
+public:
+  PimTowerScale(std::shared_ptr<PimRing> ring, const std::vector<uint64_t> &c) : ring_(std::move(ring)) {
+    if (c.size() != ring_->GetNumTowers()) throw pim_math_error("PimTowerScale: one constant per tower");
+    PimManager::check(fhe_tower_scale_create(ring_->handle(), c.data(), &plan_), "PimTowerScale");
+  }
+  ~PimTowerScale() { fhe_tower_scale_destroy(plan_); }
+  PimTowerScale(const PimTowerScale &) = delete;
+  PimTowerScale &operator=(const PimTowerScale &) = delete;
+  fhe_tower_scale *handle() const { return plan_; }
+  const std::shared_ptr<PimRing> &Ring() const { return ring_; }
+
+private:
+  std::shared_ptr<PimRing> ring_;
+  fhe_tower_scale *plan_ = nullptr;
+};
+
 class PimDCRTPoly {
 public:
   PimDCRTPoly(std::shared_ptr<PimRing> ring, size_t batch, PimFormat format, const uint64_t *host = nullptr,
@@ -273,6 +292,38 @@ public:
     PimDCRTPoly out(ringQP, batch_, resultFormat, nullptr, stream_);
     PimManager::check(fhe_expand_crt_basis(qToP.handle(), out.d_, d_, batch_, (int)format_, (int)resultFormat, stream_),
                       "ExpandCRTBasis");
+    return out;
+  }
+  /* dcrtpoly-impl.h:1361-1410 (in place in the reference): ringPQ holds the P towers first */
+  PimDCRTPoly ExpandCRTBasisReverseOrder(const PimBasis &qToP, const std::shared_ptr<PimRing> &ringPQ,
+                                         PimFormat resultFormat) const {
+    PimDCRTPoly out(ringPQ, batch_, resultFormat, nullptr, stream_);
+    PimManager::check(fhe_expand_crt_basis_reverse_order(qToP.handle(), out.d_, d_, batch_, (int)format_, (int)resultFormat,
+                                                         stream_), "ExpandCRTBasisReverseOrder");
+    return out;
+  }
+  /* dcrtpoly-impl.h:1413-1468 (in place in the reference): qToPl carries mPlQHatInvModq / qInvModp, plToQl is the exact
+   * switch back; ringQlPl = [Ql | Pl] */
+  PimDCRTPoly FastExpandCRTBasisPloverQ(const PimBasis &qToPl, const PimBasis &plToQl,
+                                        const std::shared_ptr<PimRing> &ringQlPl) const {
+    PimDCRTPoly out(ringQlPl, batch_, format_, nullptr, stream_);
+    PimManager::check(fhe_fast_expand_crt_basis_pl_over_q(qToPl.handle(), plToQl.handle(), out.d_, d_, batch_, stream_),
+                      "FastExpandCRTBasisPloverQ");
+    return out;
+  }
+  /* dcrtpoly-impl.h:1514-1534 (in place in the reference): this over the first towers of plan.Ring() */
+  PimDCRTPoly ExpandCRTBasisQlHat(const PimTowerScale &plan) const {
+    PimDCRTPoly out(plan.Ring(), batch_, format_, nullptr, stream_);
+    PimManager::check(fhe_expand_crt_basis_ql_hat(plan.handle(), (uint32_t)ring_->GetNumTowers(), out.d_, d_, batch_, stream_),
+                      "ExpandCRTBasisQlHat");
+    return out;
+  }
+  /* dcrtpoly-impl.h:2052-2066 (in place in the reference): this over plan.Ring() plus one tower */
+  PimDCRTPoly ScaleAndRoundPOverQ(const PimTowerScale &plan) const {
+    if (ring_->GetNumTowers() != plan.Ring()->GetNumTowers() + 1)
+      throw pim_math_error("ScaleAndRoundPOverQ: the input must have one tower more than the output basis");
+    PimDCRTPoly out(plan.Ring(), batch_, format_, nullptr, stream_);
+    PimManager::check(fhe_scale_and_round_p_over_q(plan.handle(), out.d_, d_, batch_, stream_), "ScaleAndRoundPOverQ");
     return out;
   }
   /* dcrtpoly-impl.h:1876-1960 */

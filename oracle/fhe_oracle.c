@@ -710,6 +710,89 @@ void orc_expand_crt_basis(const orc_ctx* Q, const orc_ctx* P, uint64_t* out, con
     free(coef); free(partP); free(hi); free(hm); free(qinv); free(aq);
 }
 
+/* DCRTPolyImpl::ExpandCRTBasisReverseOrder (dcrtpoly-impl.h:1361-1410): the same values as ExpandCRTBasis with the
+ * new towers first (temp = [partP | Q], :1381-1385). */
+void orc_expand_crt_basis_reverse(const orc_ctx* Q, const orc_ctx* P, uint64_t* out, const uint64_t* in, size_t B, int format,
+                                  int result_format) {
+    uint32_t N = Q->N, sq = Q->T, sp = P->T;
+    uint64_t* tmp = (uint64_t*)malloc(B * (size_t)(sq + sp) * N * 8);
+    orc_expand_crt_basis(Q, P, tmp, in, B, format, result_format);
+    towers_copy(out, sq + sp, 0, tmp, sq + sp, sq, sp, B, N);
+    towers_copy(out, sq + sp, sp, tmp, sq + sp, 0, sq, B, N);
+    free(tmp);
+}
+
+/* DCRTPolyImpl::FastExpandCRTBasisPloverQ (dcrtpoly-impl.h:1413-1468, HAVE_INT128 branch).  neg_pl_qhat_inv[sq] =
+ * mPlQHatInvModq and qinv_modp[sq*spl] = qInvModp as bfvrns-cryptoparameters.cpp:501-523 builds them; the second step is
+ * SwitchCRTBasis Pl -> Ql with the tables of :390-443 (orc_switch_tables / orc_exact_tables restate them).
+ * in over Q [B][sq][N] -> out over QlPl [B][sql+spl][N]; no format change. */
+void orc_fast_expand_pl_over_q(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, const uint64_t* q, uint32_t sq,
+                               const uint64_t* ql, uint32_t sql, const uint64_t* pl, uint32_t spl,
+                               const uint64_t* neg_pl_qhat_inv, const uint64_t* qinv_modp) {
+    size_t wpl = B * (size_t)spl * N, wql = B * (size_t)sql * N;
+    uint64_t* partPl = (uint64_t*)malloc(wpl * 8);
+    uint64_t* partQl = (uint64_t*)malloc(wql * 8);
+    uint64_t* hi = (uint64_t*)malloc(sizeof(uint64_t) * spl);
+    uint64_t* hm = (uint64_t*)malloc(sizeof(uint64_t) * spl * sql);
+    double* pinv = (double*)malloc(sizeof(double) * spl);
+    uint64_t* ap = (uint64_t*)malloc(sizeof(uint64_t) * (spl + 1) * sql);
+    /* :1420-1444 is the loop of ApproxSwitchCRTBasis with these two tables in the places of QHatInvModq / QHatModp */
+    orc_approx_switch(partPl, in, B, N, q, sq, pl, spl, neg_pl_qhat_inv, qinv_modp);
+    orc_switch_tables(pl, spl, ql, sql, hi, hm);
+    orc_exact_tables(pl, spl, ql, sql, pinv, ap);
+    orc_switch_crt_basis(partQl, partPl, B, N, pl, spl, ql, sql, hi, hm, pinv, ap);          /* :1448-1450 */
+    towers_copy(out, sql + spl, 0, partQl, sql, 0, sql, B, N);                                /* :1457-1465 */
+    towers_copy(out, sql + spl, sql, partPl, spl, 0, spl, B, N);
+    free(partPl); free(partQl); free(hi); free(hm); free(pinv); free(ap);
+}
+
+/* Tables of FastExpandCRTBasisPloverQ, bfvrns-cryptoparameters.cpp:501-523:
+ *   neg[i] = q_i - [Pl * (Q/q_i)^-1]_{q_i}   (m_negRlQHatInvModq),   qinv_modp[i*spl+j] = [q_i^-1]_{p_j}   (m_qInvModr) */
+void orc_pl_over_q_tables(const uint64_t* q, uint32_t sq, const uint64_t* pl, uint32_t spl, uint64_t* neg, uint64_t* qinv_modp) {
+    for (uint32_t i = 0; i < sq; i++) {
+        uint64_t qi = q[i], hat = 1 % qi, plm = 1 % qi;
+        for (uint32_t k = 0; k < sq; k++)
+            if (k != i) hat = mulmod_u128(hat, q[k] % qi, qi);
+        for (uint32_t j = 0; j < spl; j++) plm = mulmod_u128(plm, pl[j] % qi, qi);
+        neg[i] = qi - mulmod_u128(plm, orc_modinv(hat, qi), qi);
+        for (uint32_t j = 0; j < spl; j++) qinv_modp[(size_t)i * spl + j] = orc_modinv(qi % pl[j], pl[j]);
+    }
+}
+
+/* DCRTPolyImpl::ExpandCRTBasisQlHat (dcrtpoly-impl.h:1514-1534): in over the first sl towers of q [B][sl][N] -> out over
+ * q [B][sq][N]: tower i < sl times c[i] (ModMulFastConstEq), zero towers above. */
+void orc_expand_ql_hat(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, const uint64_t* q, uint32_t sq, uint32_t sl,
+                       const uint64_t* c) {
+    for (size_t b = 0; b < B; b++)
+        for (uint32_t i = 0; i < sq; i++) {
+            uint64_t* o = out + (b * sq + i) * N;
+            if (i >= sl) { memset(o, 0, (size_t)N * 8); continue; }
+            const uint64_t* x = in + (b * sl + i) * N;
+            uint64_t cp = orc_prep_mulconst(c[i], q[i]);
+            for (uint32_t n = 0; n < N; n++) o[n] = orc_modmul_const(x[n], c[i], q[i], cp);
+        }
+}
+
+/* DCRTPolyImpl::ScaleAndRoundPOverQ (dcrtpoly-impl.h:2052-2066): in over q plus one extra tower [B][sq+1][N] -> out over
+ * q: ModSubEq of the extra tower (NativeIntegerT::ModSubEq reduces an operand >= q_i first, ubintnat.h:901-912), then
+ * Times(pInvModq) (dcrtpoly-impl.h:618-627 -> a full modular multiply). */
+void orc_scale_round_p_over_q(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, const uint64_t* q, uint32_t sq,
+                              const uint64_t* pinv_modq) {
+    for (size_t b = 0; b < B; b++) {
+        const uint64_t* last = in + (b * (sq + 1) + sq) * N;
+        for (uint32_t i = 0; i < sq; i++) {
+            const uint64_t* x = in + (b * (sq + 1) + i) * N;
+            uint64_t* o = out + (b * sq + i) * N;
+            uint64_t qi = q[i];
+            for (uint32_t n = 0; n < N; n++) {
+                uint64_t av = x[n] >= qi ? x[n] % qi : x[n], bv = last[n] >= qi ? last[n] % qi : last[n];
+                uint64_t d = av >= bv ? av - bv : av + qi - bv;
+                o[n] = mulmod_u128(d, pinv_modq[i], qi);
+            }
+        }
+    }
+}
+
 void orc_scale_and_round(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, uint32_t sI, const uint64_t* o, uint32_t sO,
                          int out_last, const double* frac, const uint64_t* modo) {
     uint32_t T = sI + sO, in0 = out_last ? 0 : sO, out0 = out_last ? sI : 0;

@@ -125,6 +125,22 @@ void orc_switch_crt_basis(uint64_t* out, const uint64_t* in, size_t B, uint32_t 
 /* DCRTPolyImpl::ExpandCRTBasis (dcrtpoly-impl.h:1311-1358): in over Q (format 0/1) -> out over QP in result_format */
 void orc_expand_crt_basis(const orc_ctx* Q, const orc_ctx* P, uint64_t* out, const uint64_t* in, size_t B, int format,
                           int result_format);
+/* DCRTPolyImpl::ExpandCRTBasisReverseOrder (dcrtpoly-impl.h:1361-1410): out over PQ (new towers first) */
+void orc_expand_crt_basis_reverse(const orc_ctx* Q, const orc_ctx* P, uint64_t* out, const uint64_t* in, size_t B, int format,
+                                  int result_format);
+/* ---- BFV HPSPOVERQ / HPSPOVERQLEVELED set ----
+ * DCRTPolyImpl::FastExpandCRTBasisPloverQ (dcrtpoly-impl.h:1413-1468): in over q -> out over [ql | pl], tables
+ * neg_pl_qhat_inv[sq], qinv_modp[sq][spl] from the scheme (bfvrns-cryptoparameters.cpp:501-523) */
+void orc_fast_expand_pl_over_q(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, const uint64_t* q, uint32_t sq,
+                               const uint64_t* ql, uint32_t sql, const uint64_t* pl, uint32_t spl,
+                               const uint64_t* neg_pl_qhat_inv, const uint64_t* qinv_modp);
+void orc_pl_over_q_tables(const uint64_t* q, uint32_t sq, const uint64_t* pl, uint32_t spl, uint64_t* neg, uint64_t* qinv_modp);
+/* DCRTPolyImpl::ExpandCRTBasisQlHat (dcrtpoly-impl.h:1514-1534) */
+void orc_expand_ql_hat(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, const uint64_t* q, uint32_t sq, uint32_t sl,
+                       const uint64_t* c);
+/* DCRTPolyImpl::ScaleAndRoundPOverQ (dcrtpoly-impl.h:2052-2066) */
+void orc_scale_round_p_over_q(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, const uint64_t* q, uint32_t sq,
+                              const uint64_t* pinv_modq);
 /* DCRTPolyImpl::ScaleAndRound(paramsOutput, ...) (dcrtpoly-impl.h:1876-1960, HAVE_INT128 branch): in over
  * [B][sI+sO][N]; the output moduli o[sO] are the LAST sO towers when out_last != 0 (input index 0), else the first
  * (input index sO).  frac[sI], modo[sO][sI+1] row-major as the scheme precomputes them. */

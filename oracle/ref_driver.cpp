@@ -454,6 +454,110 @@ int ref_polys_expand_crt_basis(ref_polys* a, ref_ctx* P, ref_ctx* QP, int result
     return rc;
 }
 
+// DCRTPoly::ExpandCRTBasisReverseOrder (dcrtpoly-impl.h:1361-1410), in place: Q -> PQ (the P towers first)
+int ref_polys_expand_crt_basis_reverse(ref_polys* a, ref_ctx* P, ref_ctx* PQ, int result_format) {
+    int rc = 0;
+    std::string err;
+    serial_omp([&] {
+        try {
+            auto t = make_exact_tables(moduli_of(a->ctx), moduli_of(P));
+            for (auto& poly : a->v)
+                poly.ExpandCRTBasisReverseOrder(PQ->params, P->params, t.sw.hatInv, t.sw.hatInvPrecon, t.hatModpT, t.alphaQModp, t.sw.mu,
+                                                t.qInv, result_format == 0 ? Format::EVALUATION : Format::COEFFICIENT);
+            a->ctx = PQ;
+        }
+        catch (const std::exception& e) { err = e.what(); rc = 1; }
+    });
+    if (rc) g_ref_err = err;
+    return rc;
+}
+
+// ---- BFV HPSPOVERQ / HPSPOVERQLEVELED set -----------------------------------------------------------------
+// Tables of FastExpandCRTBasisPloverQ as src/pke/lib/scheme/bfvrns/bfvrns-cryptoparameters.cpp:501-523 builds them:
+//   mNegRlQHatInvModq[i] = q_i - [Rl * (Q/q_i)^-1]_{q_i},  qInvModr[i][j] = [q_i^-1]_{r_j}
+static void make_pl_over_q_tables(const std::vector<NativeInteger>& mq, const std::vector<NativeInteger>& mpl,
+                                  std::vector<NativeInteger>& neg, std::vector<NativeInteger>& negPrecon,
+                                  std::vector<std::vector<NativeInteger>>& qInvModp) {
+    BigInteger Q(1), Pl(1);
+    for (auto& q : mq) Q *= BigInteger(q);
+    for (auto& r : mpl) Pl *= BigInteger(r);
+    neg.resize(mq.size()); negPrecon.resize(mq.size()); qInvModp.resize(mq.size());
+    for (size_t i = 0; i < mq.size(); i++) {
+        BigInteger QHati        = Q / BigInteger(mq[i]);
+        BigInteger QHatInvModqi = QHati.ModInverse(BigInteger(mq[i]));
+        neg[i]                  = Pl.ModMul(QHatInvModqi, BigInteger(mq[i])).ConvertToInt();
+        neg[i]                  = mq[i].Sub(neg[i]);
+        negPrecon[i]            = neg[i].PrepModMulConst(mq[i]);
+        qInvModp[i].resize(mpl.size());
+        for (size_t j = 0; j < mpl.size(); j++) qInvModp[i][j] = mq[i].ModInverse(mpl[j]);
+    }
+}
+void ref_pl_over_q_tables_get(const ref_ctx* Q, const ref_ctx* Pl, uint64_t* neg, uint64_t* qinv_modp) {
+    std::vector<NativeInteger> n, np;
+    std::vector<std::vector<NativeInteger>> qi;
+    make_pl_over_q_tables(moduli_of(Q), moduli_of(Pl), n, np, qi);
+    for (size_t i = 0; i < n.size(); i++) {
+        neg[i] = n[i].ConvertToInt();
+        for (size_t j = 0; j < qi[i].size(); j++) qinv_modp[i * qi[i].size() + j] = qi[i][j].ConvertToInt();
+    }
+}
+// DCRTPoly::FastExpandCRTBasisPloverQ (dcrtpoly-impl.h:1413-1468), in place: Q -> QlPl
+int ref_polys_fast_expand_pl_over_q(ref_polys* a, ref_ctx* Ql, ref_ctx* Pl, ref_ctx* QlPl) {
+    int rc = 0;
+    std::string err;
+    serial_omp([&] {
+        try {
+            auto mq = moduli_of(a->ctx), mpl = moduli_of(Pl), mql = moduli_of(Ql);
+            std::vector<NativeInteger> neg, negPrecon;
+            std::vector<std::vector<NativeInteger>> qInvModp;
+            make_pl_over_q_tables(mq, mpl, neg, negPrecon, qInvModp);
+            auto modpMu = make_switch_tables(mq, mpl).mu;
+            auto back   = make_exact_tables(mpl, mql);      // Pl -> Ql: bfvrns-cryptoparameters.cpp:390-443
+            DCRTPoly::CRTBasisExtensionPrecomputations pre(QlPl->params, Pl->params, Ql->params, neg, negPrecon, qInvModp, modpMu,
+                                                           back.sw.hatInv, back.sw.hatInvPrecon, back.hatModpT, back.alphaQModp,
+                                                           back.sw.mu, back.qInv);
+            for (auto& poly : a->v) poly.FastExpandCRTBasisPloverQ(pre);
+            a->ctx = QlPl;
+        }
+        catch (const std::exception& e) { err = e.what(); rc = 1; }
+    });
+    if (rc) g_ref_err = err;
+    return rc;
+}
+// DCRTPoly::ExpandCRTBasisQlHat (dcrtpoly-impl.h:1514-1534), in place: Ql (the first towers of Q) -> Q; c[i] < q_i
+int ref_polys_expand_ql_hat(ref_polys* a, ref_ctx* Q, const uint64_t* c) {
+    int rc = 0;
+    std::string err;
+    serial_omp([&] {
+        try {
+            auto mq = moduli_of(Q);
+            std::vector<NativeInteger> k(a->ctx->T), kp(a->ctx->T);
+            for (uint32_t i = 0; i < a->ctx->T; i++) { k[i] = NativeInteger(c[i]); kp[i] = k[i].PrepModMulConst(mq[i]); }
+            for (auto& poly : a->v) poly.ExpandCRTBasisQlHat(Q->params, k, kp, Q->T);
+            a->ctx = Q;
+        }
+        catch (const std::exception& e) { err = e.what(); rc = 1; }
+    });
+    if (rc) g_ref_err = err;
+    return rc;
+}
+// DCRTPoly::ScaleAndRoundPOverQ (dcrtpoly-impl.h:2052-2066), in place: Q plus one tower -> Q
+int ref_polys_scale_round_p_over_q(ref_polys* a, ref_ctx* Q, const uint64_t* pinv_modq) {
+    int rc = 0;
+    std::string err;
+    serial_omp([&] {
+        try {
+            std::vector<NativeInteger> k(Q->T);
+            for (uint32_t i = 0; i < Q->T; i++) k[i] = NativeInteger(pinv_modq[i]);
+            for (auto& poly : a->v) poly.ScaleAndRoundPOverQ(Q->params, k);
+            a->ctx = Q;
+        }
+        catch (const std::exception& e) { err = e.what(); rc = 1; }
+    });
+    if (rc) g_ref_err = err;
+    return rc;
+}
+
 // ScaleAndRound tables for the HPS multiplication, t * R / (Q*R) from QR down to R (bfvrns-cryptoparameters.cpp:278-311):
 // frac [sizeQ], modr [sizeR][sizeQ+1] (row-major)
 static void make_scale_tables(const std::vector<NativeInteger>& mq, const std::vector<NativeInteger>& mr, uint64_t tval,

@@ -208,6 +208,19 @@ static void test_dcrtpoly_ext(uint32_t N, uint32_t sq, uint32_t sp, size_t B) {
     orc_scale_and_round(e6.data(), hy.data(), B, N, sq, q.data() + sq, sp, 1, frac.data(), modo.data());
     PimScaleRound sr(ring, sp, true, frac, modo);
     EXPECT(y.ScaleAndRound(sr).GetValues() == e6, "ScaleAndRound N=%u", N);
+    // BFV HPSPOVERQ tails: ExpandCRTBasisQlHat (Q as the first towers of QP) and ScaleAndRoundPOverQ (QP minus its last tower)
+    std::vector<uint64_t> cst(T), e7(B * T * (size_t)N), e8(B * (T - 1) * (size_t)N);
+    for (uint32_t i = 0; i < T; i++) cst[i] = orc_uniform_at(77, i, q[i]);
+    orc_expand_ql_hat(e7.data(), hx.data(), B, N, q.data(), T, sq, cst.data());
+    PimTowerScale hat(ring, cst);
+    PimDCRTPoly eh = x.ExpandCRTBasisQlHat(hat);
+    EXPECT(eh.GetParams()->GetNumTowers() == T && eh.GetValues() == e7, "ExpandCRTBasisQlHat N=%u", N);
+    orc_scale_round_p_over_q(e8.data(), hy.data(), B, N, q.data(), T - 1, cst.data());
+    PimTowerScale pov(PimRing::View(ring, 0, T - 1), std::vector<uint64_t>(cst.begin(), cst.end() - 1));
+    EXPECT(y.ScaleAndRoundPOverQ(pov).GetValues() == e8, "ScaleAndRoundPOverQ N=%u", N);
+    threw = false;
+    try { x.ScaleAndRoundPOverQ(pov); } catch (const std::exception&) { threw = true; }
+    EXPECT(threw || sq == T, "ScaleAndRoundPOverQ must reject an input without the extra tower");
     for (orc_ctx* c : {oQP, oQ, oP, oR, oL}) orc_ctx_destroy(c);
 }
 

@@ -54,6 +54,11 @@ class Oracle:
             ("orc_switch_crt_basis", None, [vp, vp, sz, u32, vp, u32, vp, u32, vp, vp, vp, vp]),
             ("orc_expand_crt_basis", None, [vp, vp, vp, vp, sz, ci, ci]),
             ("orc_scale_and_round", None, [vp, vp, sz, u32, u32, vp, u32, ci, vp, vp]),
+            ("orc_expand_crt_basis_reverse", None, [vp, vp, vp, vp, sz, ci, ci]),
+            ("orc_pl_over_q_tables", None, [vp, u32, vp, u32, vp, vp]),
+            ("orc_fast_expand_pl_over_q", None, [vp, vp, sz, u32, vp, u32, vp, u32, vp, u32, vp, vp]),
+            ("orc_expand_ql_hat", None, [vp, vp, sz, u32, vp, u32, u32, vp]),
+            ("orc_scale_round_p_over_q", None, [vp, vp, sz, u32, vp, u32, vp]),
             ("orc_uniform_at", u64, [u64, u64, u64]), ("orc_fill_uniform", None, [vp, sz, u64, u64, u64]),
         ]:
             f = getattr(L, name)
@@ -268,6 +273,61 @@ OracleBasis.exact_tables = _exact_tables
 OracleBasis.switch_exact = _switch_exact
 OracleBasis.expand = _expand
 OracleBasis.scale_and_round = _scale_and_round
+
+
+def _expand_reverse(self, x, fmt, result_fmt):
+    """ExpandCRTBasisReverseOrder: [B][Q][N] -> [B][P+Q][N], the P towers first."""
+    x = np.ascontiguousarray(x, np.uint64)
+    B = x.size // (self.sq * self.n)
+    out = np.empty((B, self.sq + self.sp, self.n), np.uint64)
+    self.o.L.orc_expand_crt_basis_reverse(self.Q.h, self.P.h, _p(out), _p(x), B, fmt, result_fmt)
+    return out
+
+
+OracleBasis.expand_reverse = _expand_reverse
+
+
+def _pl_over_q_tables(self, q, pl):
+    """m_negRlQHatInvModq [sq] and m_qInvModr [sq][spl] (bfvrns-cryptoparameters.cpp:501-523)."""
+    q, pl = np.ascontiguousarray(q, np.uint64), np.ascontiguousarray(pl, np.uint64)
+    neg, qi = np.empty(len(q), np.uint64), np.empty((len(q), len(pl)), np.uint64)
+    self.L.orc_pl_over_q_tables(_p(q), len(q), _p(pl), len(pl), _p(neg), _p(qi))
+    return neg, qi
+
+
+def _fast_expand_pl_over_q(self, x, n, q, ql, pl):
+    """FastExpandCRTBasisPloverQ: [B][len(q)][N] -> [B][len(ql)+len(pl)][N]."""
+    q, ql, pl = (np.ascontiguousarray(v, np.uint64) for v in (q, ql, pl))
+    neg, qi = self.pl_over_q_tables(q, pl)
+    x = np.ascontiguousarray(x, np.uint64)
+    B = x.size // (len(q) * n)
+    out = np.empty((B, len(ql) + len(pl), n), np.uint64)
+    self.L.orc_fast_expand_pl_over_q(_p(out), _p(x), B, n, _p(q), len(q), _p(ql), len(ql), _p(pl), len(pl), _p(neg), _p(qi))
+    return out
+
+
+def _expand_ql_hat(self, x, n, q, sl, c):
+    q, c = np.ascontiguousarray(q, np.uint64), np.ascontiguousarray(c, np.uint64)
+    x = np.ascontiguousarray(x, np.uint64)
+    B = x.size // (sl * n)
+    out = np.empty((B, len(q), n), np.uint64)
+    self.L.orc_expand_ql_hat(_p(out), _p(x), B, n, _p(q), len(q), sl, _p(c))
+    return out
+
+
+def _scale_round_p_over_q(self, x, n, q, pinv_modq):
+    q, c = np.ascontiguousarray(q, np.uint64), np.ascontiguousarray(pinv_modq, np.uint64)
+    x = np.ascontiguousarray(x, np.uint64)
+    B = x.size // ((len(q) + 1) * n)
+    out = np.empty((B, len(q), n), np.uint64)
+    self.L.orc_scale_round_p_over_q(_p(out), _p(x), B, n, _p(q), len(q), _p(c))
+    return out
+
+
+Oracle.pl_over_q_tables = _pl_over_q_tables
+Oracle.fast_expand_pl_over_q = _fast_expand_pl_over_q
+Oracle.expand_ql_hat = _expand_ql_hat
+Oracle.scale_round_p_over_q = _scale_round_p_over_q
 
 
 def _rescale(self, n, q, psi, x, fmt, t=0):

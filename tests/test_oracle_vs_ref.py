@@ -48,6 +48,11 @@ def ref():
     R.ref_scale_tables_get.argtypes = [vp, vp, u64, vp, vp]
     R.ref_polys_scale_and_round.restype = vp
     R.ref_polys_scale_and_round.argtypes = [vp, vp, vp, u64]
+    R.ref_polys_expand_crt_basis_reverse.argtypes = [vp, vp, vp, ci]
+    R.ref_pl_over_q_tables_get.argtypes = [vp, vp, vp, vp]
+    R.ref_polys_fast_expand_pl_over_q.argtypes = [vp, vp, vp, vp]
+    R.ref_polys_expand_ql_hat.argtypes = [vp, vp, vp]
+    R.ref_polys_scale_round_p_over_q.argtypes = [vp, vp, vp]
     R.ref_bfv_hps_mult.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp)]
     return R
 
@@ -253,3 +258,84 @@ def test_bfv_hps_mult_core_matches_reference(oracle, ref, nbits, n, sq, sr, t):
         ref.ref_polys_free(h)
     for c in (cQ, cR, cQR):
         ref.ref_ctx_destroy(c)
+
+
+@pytest.mark.parametrize("nbits,n,sq,sp", [(30, 16, 2, 3), (60, 256, 3, 2), (60, 1 << 11, 4, 5)])
+def test_expand_reverse_order_matches_reference(oracle, ref, nbits, n, sq, sp):
+    """DCRTPolyImpl::ExpandCRTBasisReverseOrder (dcrtpoly-impl.h:1361-1410) on the reference's own DCRTPoly."""
+    q, psi = oracle.gen_params(nbits, n, sq + sp)
+    ob = oracle.basis(n, q, psi, sq)
+    pq, ppsi = np.concatenate([q[sq:], q[:sq]]), np.concatenate([psi[sq:], psi[:sq]])
+    cQ = ref.ref_ctx_create(n, sq, p(q[:sq].copy()), p(psi[:sq].copy()))
+    cP = ref.ref_ctx_create(n, sp, p(q[sq:].copy()), p(psi[sq:].copy()))
+    cPQ = ref.ref_ctx_create(n, sq + sp, p(pq), p(ppsi))
+    B = 2
+    x = oracle.fill_ring(B, n, q[:sq].copy(), 71)
+    x[0, :, 0] = q[:sq] - 1
+    for fmt in (0, 1):
+        for rf in (0, 1):
+            hx = ref.ref_polys_load(cQ, p(x), B, fmt)
+            assert ref.ref_polys_expand_crt_basis_reverse(hx, cP, cPQ, rf) == 0, ref.ref_last_error()
+            res = np.empty((B, sq + sp, n), np.uint64)
+            ref.ref_polys_store(hx, p(res))
+            assert np.array_equal(res, ob.expand_reverse(x, fmt, rf)), f"ExpandCRTBasisReverseOrder {fmt}->{rf}"
+            ref.ref_polys_free(hx)
+    for c in (cQ, cP, cPQ):
+        ref.ref_ctx_destroy(c)
+
+
+@pytest.mark.parametrize("nbits,n,sq,sl", [(30, 16, 2, 2), (60, 256, 3, 2), (60, 1 << 11, 5, 5), (45, 64, 4, 1)])
+def test_hps_p_over_q_set_matches_reference(oracle, ref, nbits, n, sq, sl):
+    """FastExpandCRTBasisPloverQ (tables and values), ExpandCRTBasisQlHat and ScaleAndRoundPOverQ
+    (dcrtpoly-impl.h:1413-1468, 1514-1534, 2052-2066) on the reference's own DCRTPoly."""
+    allq, allpsi = oracle.gen_params(nbits, n, sq + sl)
+    q, psi, pl, plpsi = allq[:sq].copy(), allpsi[:sq].copy(), allq[sq:].copy(), allpsi[sq:].copy()
+    ql, qlpsi = q[:sl].copy(), psi[:sl].copy()
+    cQ = ref.ref_ctx_create(n, sq, p(q), p(psi))
+    cQl = ref.ref_ctx_create(n, sl, p(ql), p(qlpsi))
+    cPl = ref.ref_ctx_create(n, sl, p(pl), p(plpsi))
+    qlpl, qlplpsi = np.concatenate([ql, pl]), np.concatenate([qlpsi, plpsi])
+    cQlPl = ref.ref_ctx_create(n, 2 * sl, p(qlpl), p(qlplpsi))
+    neg, qi = np.empty(sq, np.uint64), np.empty((sq, sl), np.uint64)
+    ref.ref_pl_over_q_tables_get(cQ, cPl, p(neg), p(qi))
+    oneg, oqi = oracle.pl_over_q_tables(q, pl)
+    assert np.array_equal(neg, oneg) and np.array_equal(qi, oqi)
+    B = 2
+    x = oracle.fill_ring(B, n, q, 81)
+    x[0, :, 0] = q - 1
+    x[0, :, 1] = 0
+    hx = ref.ref_polys_load(cQ, p(x), B, 1)
+    assert ref.ref_polys_fast_expand_pl_over_q(hx, cQl, cPl, cQlPl) == 0, ref.ref_last_error()
+    res = np.empty((B, 2 * sl, n), np.uint64)
+    ref.ref_polys_store(hx, p(res))
+    assert np.array_equal(res, oracle.fast_expand_pl_over_q(x, n, q, ql, pl))
+    ref.ref_polys_free(hx)
+    # ExpandCRTBasisQlHat: Ql -> Q with arbitrary reduced constants
+    rng = np.random.default_rng(5)
+    c = np.array([int(rng.integers(0, int(ql[i]))) for i in range(sl)], np.uint64)
+    y = oracle.fill_ring(B, n, ql, 82)
+    y[0, :, 0] = ql - 1
+    hy = ref.ref_polys_load(cQl, p(y), B, 0)
+    assert ref.ref_polys_expand_ql_hat(hy, cQ, p(c)) == 0, ref.ref_last_error()
+    res = np.empty((B, sq, n), np.uint64)
+    ref.ref_polys_store(hy, p(res))
+    assert np.array_equal(res, oracle.expand_ql_hat(y, n, q, sl, c))
+    ref.ref_polys_free(hy)
+    # ScaleAndRoundPOverQ: the extra tower smaller than every q_i (the chain's next prime) and larger (the chain's first)
+    for qs, ps, extra, epsi in ((q, psi, pl[0], plpsi[0]), (allq[1:sq + 1].copy(), allpsi[1:sq + 1].copy(), allq[0], allpsi[0])):
+        full, fpsi = np.append(qs, extra).astype(np.uint64), np.append(ps, epsi).astype(np.uint64)
+        cq = ref.ref_ctx_create(n, sq, p(qs), p(ps))
+        cf = ref.ref_ctx_create(n, sq + 1, p(full), p(fpsi))
+        k = np.array([int(rng.integers(0, int(qs[i]))) for i in range(sq)], np.uint64)
+        z = oracle.fill_ring(B, n, full, 83)
+        z[0, :, 0] = full - 1
+        z[0, :, 1] = 0
+        hz = ref.ref_polys_load(cf, p(z), B, 1)
+        assert ref.ref_polys_scale_round_p_over_q(hz, cq, p(k)) == 0, ref.ref_last_error()
+        res = np.empty((B, sq, n), np.uint64)
+        ref.ref_polys_store(hz, p(res))
+        assert np.array_equal(res, oracle.scale_round_p_over_q(z, n, qs, k))
+        ref.ref_polys_free(hz)
+        ref.ref_ctx_destroy(cq); ref.ref_ctx_destroy(cf)
+    for cc in (cQ, cQl, cPl, cQlPl):
+        ref.ref_ctx_destroy(cc)

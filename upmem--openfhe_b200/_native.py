@@ -63,6 +63,12 @@ SIGNATURES = {
     "fhe_approx_mod_down": (ci, [vp, u64, u64, sz, u64, ci]),
     "fhe_switch_crt_basis": (ci, [vp, u64, u64, sz, ci]),
     "fhe_expand_crt_basis": (ci, [vp, u64, u64, sz, ci, ci, ci]),
+    "fhe_expand_crt_basis_reverse_order": (ci, [vp, u64, u64, sz, ci, ci, ci]),
+    "fhe_fast_expand_crt_basis_pl_over_q": (ci, [vp, vp, u64, u64, sz, ci]),
+    "fhe_tower_scale_create": (ci, [vp, vp, ctypes.POINTER(vp)]),
+    "fhe_tower_scale_destroy": (ci, [vp]),
+    "fhe_expand_crt_basis_ql_hat": (ci, [vp, u32, u64, u64, sz, ci]),
+    "fhe_scale_and_round_p_over_q": (ci, [vp, u64, u64, sz, ci]),
     "fhe_scale_round_create": (ci, [vp, u32, ci, vp, vp, ctypes.POINTER(vp)]),
     "fhe_scale_round_destroy": (ci, [vp]),
     "fhe_scale_and_round": (ci, [vp, u64, u64, sz, ci]),

@@ -534,4 +534,81 @@ cudaError_t launch_rescale_spread(uint64_t* tmp, const uint64_t* last, size_t ba
     return cudaGetLastError();
 }
 
+
+// ---- BFV HPSPOVERQ tails ----------------------------------------------------------------------------------------
+// One thread per coefficient pair of one batch item, towers in a loop (every row segment is contiguous in n).
+// k[i] = {c_i, c_i', one_i' = floor(2^64 / q_i), -}.
+//   mode 0 (ExpandCRTBasisQlHat, dcrtpoly-impl.h:1514-1534): x over [B][sl][N] -> out over [B][T][N]:
+//          out_i = x_i * c_i (i < sl), 0 (sl <= i < T)
+//   mode 1 (ScaleAndRoundPOverQ, dcrtpoly-impl.h:2052-2066): x over [B][T+1][N] -> out over [B][T][N]:
+//          out_i = (x_i - (x_T mod q_i)) * c_i; the last tower's residue can exceed q_i, ModSubEq reduces it first
+template <int MODE>
+__global__ void __launch_bounds__(256)
+tower_scale_kernel(u64* __restrict__ out, const u64* __restrict__ x, size_t npairs, u32 logN, u32 sl, u32 T,
+                   const TowerMod* __restrict__ mods, const ulonglong4* __restrict__ k) {
+    const u32 xT = MODE == 0 ? sl : T + 1;
+    for (size_t p = (size_t)blockIdx.x * 256 + threadIdx.x; p < npairs; p += (size_t)gridDim.x * 256) {
+        size_t e = 2 * p;
+        size_t b = e >> logN;
+        u32 n = (u32)e & ((1u << logN) - 1);
+        const u64* xb = x + ((b * xT) << logN) + n;
+        u64* ob = out + ((b * T) << logN) + n;
+        ulonglong2 last = make_ulonglong2(0, 0);
+        if (MODE == 1) last = *reinterpret_cast<const ulonglong2*>(xb + ((size_t)T << logN));
+        for (u32 i = 0; i < T; i++) {
+            ulonglong2 r = make_ulonglong2(0, 0);
+            if (MODE == 1 || i < sl) {
+                const u64 q = mods[i].q;
+                const ulonglong4 c = k[i];
+                ulonglong2 xv = *reinterpret_cast<const ulonglong2*>(xb + ((size_t)i << logN));
+                if (MODE == 1) {
+                    xv.x = submod(xv.x, shoup(last.x, 1, c.z, q), q);
+                    xv.y = submod(xv.y, shoup(last.y, 1, c.z, q), q);
+                }
+                r = make_ulonglong2(shoup(xv.x, c.x, c.y, q), shoup(xv.y, c.x, c.y, q));
+            }
+            *reinterpret_cast<ulonglong2*>(ob + ((size_t)i << logN)) = r;
+        }
+    }
+}
+
+// scalar form for N = 1
+template <int MODE>
+__global__ void tower_scale_scalar_kernel(u64* __restrict__ out, const u64* __restrict__ x, size_t batch, u32 sl, u32 T,
+                                          const TowerMod* __restrict__ mods, const ulonglong4* __restrict__ k) {
+    const u32 xT = MODE == 0 ? sl : T + 1;
+    for (size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x; b < batch; b += (size_t)gridDim.x * blockDim.x)
+        for (u32 i = 0; i < T; i++) {
+            u64 r = 0;
+            if (MODE == 1 || i < sl) {
+                const u64 q = mods[i].q;
+                const ulonglong4 c = k[i];
+                u64 xv = x[b * xT + i];
+                if (MODE == 1) xv = submod(xv, shoup(x[b * xT + T], 1, c.z, q), q);
+                r = shoup(xv, c.x, c.y, q);
+            }
+            out[b * T + i] = r;
+        }
+}
+
+cudaError_t launch_tower_scale(int mode, uint64_t* out, const uint64_t* x, size_t batch, uint32_t logN, uint32_t sl,
+                               uint32_t T, const TowerMod* mods, const ulonglong4* k, cudaStream_t st) {
+    if (batch == 0 || T == 0) return cudaSuccess;
+    u64* o = reinterpret_cast<u64*>(out);
+    const u64* xx = reinterpret_cast<const u64*>(x);
+    if (logN == 0) {
+        unsigned grid = (unsigned)((batch + 255) / 256 > 4096 ? 4096 : (batch + 255) / 256);
+        if (mode == 0) tower_scale_scalar_kernel<0><<<grid, 256, 0, st>>>(o, xx, batch, sl, T, mods, k);
+        else tower_scale_scalar_kernel<1><<<grid, 256, 0, st>>>(o, xx, batch, sl, T, mods, k);
+    } else {
+        size_t npairs = (batch << logN) / 2;
+        size_t g = (npairs + 255) / 256;
+        unsigned grid = (unsigned)(g > 148 * 64 ? 148 * 64 : g);
+        if (mode == 0) tower_scale_kernel<0><<<grid, 256, 0, st>>>(o, xx, npairs, logN, sl, T, mods, k);
+        else tower_scale_kernel<1><<<grid, 256, 0, st>>>(o, xx, npairs, logN, sl, T, mods, k);
+    }
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
+}
+
 }  // namespace fhe

@@ -88,6 +88,8 @@ cudaError_t launch_scale_round(const ScaleDev& sd, uint64_t* dst, const uint64_t
 cudaError_t launch_tower_affine(int mode, uint64_t* out, const uint64_t* x, const uint64_t* v, size_t batch, uint32_t logN,
                                 uint32_t l, uint32_t xT, const TowerMod* mods, const ulonglong4* k, cudaStream_t st);
 // tmp[b][i][n] = SwitchModulus(last[b][n], ql -> q_i) (* c_i), see basis.cu
+cudaError_t launch_tower_scale(int mode, uint64_t* out, const uint64_t* x, size_t batch, uint32_t logN, uint32_t sl,
+                               uint32_t T, const TowerMod* mods, const ulonglong4* k, cudaStream_t st);
 cudaError_t launch_rescale_spread(uint64_t* tmp, const uint64_t* last, size_t batch, uint32_t logN, uint32_t l, uint64_t ql,
                                   const ulonglong4* sw, const ulonglong4* k, ulonglong2 pre, int bgv, cudaStream_t st);
 // Counter-based uniform fill in [0, q_t) per tower (same definition as the test oracle's generator).

@@ -1196,38 +1196,131 @@ extern "C" int fhe_switch_crt_basis(fhe_basis* b, fhe_dptr dst, fhe_dptr src, si
     return FHE_OK;
 }
 
-extern "C" int fhe_expand_crt_basis(fhe_basis* b, fhe_dptr dst_qp, fhe_dptr src_q, size_t batch, int format, int result_format,
-                                    int stream) {
+// ExpandCRTBasis (reverse = false: towers [Q | P]) and ExpandCRTBasisReverseOrder (reverse = true: [P | Q])
+static int expand_run(fhe_basis* b, fhe_dptr dst_, fhe_dptr src_q, size_t batch, int format, int result_format, int stream,
+                      bool reverse, const char* who) {
     if (!b) return fail(FHE_EINVAL, "null basis");
     cudaStream_t s;
     int rc = ring_stream(b->from, stream, &s);
     if (rc) return rc;
     if ((format != 0 && format != 1) || (result_format != 0 && result_format != 1))
-        return fail(FHE_EINVAL, "fhe_expand_crt_basis: formats must be 0 or 1");
+        return fail(FHE_EINVAL, "%s: formats must be 0 or 1", who);
     if (batch == 0) return FHE_OK;
-    if (!dst_qp || !src_q) return fail(FHE_EINVAL, "fhe_expand_crt_basis: null device pointer");
+    if (!dst_ || !src_q) return fail(FHE_EINVAL, "%s: null device pointer", who);
     if ((rc = basis_exact_ready(b))) return rc;
     const uint32_t N = b->from->dev.N, logN = b->from->dev.logN, sq = b->dev.sq, sp = b->dev.sp;
-    uint64_t* dst = (uint64_t*)(uintptr_t)dst_qp;
+    const uint32_t q0 = reverse ? sp : 0, p0 = reverse ? 0 : sq;                               // first tower of each part
+    uint64_t* dst = (uint64_t*)(uintptr_t)dst_;
     const uint64_t* src = (const uint64_t*)(uintptr_t)src_q;
     const size_t wq = batch * sq * (size_t)N;
-    const char* who = "fhe_expand_crt_basis";
     const uint64_t* coef = src;
     if (format == 0) {                                                                         // dcrtpoly-impl.h:1321-1324
         if ((rc = b->s0.need(b->ctx, wq * 8))) return rc;
         if ((rc = ring_ntt(b->from, (uint64_t*)b->s0.p, batch, true, s, who, src))) return rc;
         coef = (const uint64_t*)b->s0.p;
     }
-    CUDA_TRY(launch_basis_switch(b->dev, dst, sq + sp, sq, coef, sq, 0, batch, logN, true, s));          // :1326-1327
-    if (result_format == 0 && (rc = ring_ntt(b->to, dst + (size_t)sq * N, batch, false, s, who, nullptr, sq + sp))) return rc;  // :1338-1341
+    CUDA_TRY(launch_basis_switch(b->dev, dst, sq + sp, p0, coef, sq, 0, batch, logN, true, s));          // :1326-1327
+    if (result_format == 0 && (rc = ring_ntt(b->to, dst + (size_t)p0 * N, batch, false, s, who, nullptr, sq + sp))) return rc;  // :1338-1341
     if (result_format == 0 && format == 0) {
-        CUDA_TRY(copy_towers(dst, sq + sp, 0, src, sq, 0, sq, batch, N, s));                   // :1346-1349
+        CUDA_TRY(copy_towers(dst, sq + sp, q0, src, sq, 0, sq, batch, N, s));                  // :1346-1349
     } else if (result_format == 0) {
-        if ((rc = ring_ntt(b->from, dst, batch, false, s, who, src, sq + sp, sq))) return rc;  // :1350-1355
+        if ((rc = ring_ntt(b->from, dst + (size_t)q0 * N, batch, false, s, who, src, sq + sp, sq))) return rc;  // :1350-1355
     } else {
-        CUDA_TRY(copy_towers(dst, sq + sp, 0, coef, sq, 0, sq, batch, N, s));                  // COEFFICIENT result keeps coef
+        CUDA_TRY(copy_towers(dst, sq + sp, q0, coef, sq, 0, sq, batch, N, s));                 // COEFFICIENT result keeps coef
     }
     return FHE_OK;
+}
+
+extern "C" int fhe_expand_crt_basis(fhe_basis* b, fhe_dptr dst_qp, fhe_dptr src_q, size_t batch, int format, int result_format,
+                                    int stream) {
+    return expand_run(b, dst_qp, src_q, batch, format, result_format, stream, false, "fhe_expand_crt_basis");
+}
+extern "C" int fhe_expand_crt_basis_reverse_order(fhe_basis* b, fhe_dptr dst_pq, fhe_dptr src_q, size_t batch, int format,
+                                                  int result_format, int stream) {
+    return expand_run(b, dst_pq, src_q, batch, format, result_format, stream, true, "fhe_expand_crt_basis_reverse_order");
+}
+
+// DCRTPolyImpl::FastExpandCRTBasisPloverQ (dcrtpoly-impl.h:1413-1468): the Pl towers are produced where they belong in
+// dst (:1420-1444, the approximate switch with the scheme's [-Pl*(Q/q_i)^-1]_{q_i} and [q_i^-1]_{p_j}), and the exact
+// switch Pl -> Ql (:1448-1450) reads them there and fills the first towers.
+extern "C" int fhe_fast_expand_crt_basis_pl_over_q(fhe_basis* q2pl, fhe_basis* pl2ql, fhe_dptr dst_qlpl, fhe_dptr src_q,
+                                                   size_t batch, int stream) {
+    const char* who = "fhe_fast_expand_crt_basis_pl_over_q";
+    if (!q2pl || !pl2ql) return fail(FHE_EINVAL, "null basis");
+    if (q2pl->ctx != pl2ql->ctx || q2pl->from->dev.N != pl2ql->from->dev.N)
+        return fail(FHE_EINVAL, "%s: the two bases must share context and ring dimension", who);
+    if (q2pl->to->q != pl2ql->from->q) return fail(FHE_EINVAL, "%s: the second basis must start at the first one's target moduli", who);
+    cudaStream_t s;
+    int rc = ring_stream(q2pl->from, stream, &s);
+    if (rc) return rc;
+    if (batch == 0) return FHE_OK;
+    if (!dst_qlpl || !src_q) return fail(FHE_EINVAL, "%s: null device pointer", who);
+    if ((rc = basis_exact_ready(pl2ql))) return rc;
+    const uint32_t logN = q2pl->from->dev.logN, sq = q2pl->dev.sq, spl = q2pl->dev.sp, sql = pl2ql->dev.sp;
+    uint64_t* dst = (uint64_t*)(uintptr_t)dst_qlpl;
+    CUDA_TRY(launch_basis_switch(q2pl->dev, dst, sql + spl, sql, (const uint64_t*)(uintptr_t)src_q, sq, 0, batch, logN, false, s));
+    CUDA_TRY(launch_basis_switch(pl2ql->dev, dst, sql + spl, 0, dst, sql + spl, sql, batch, logN, true, s));
+    return FHE_OK;
+}
+
+struct fhe_tower_scale {
+    fhe_ctx* ctx = nullptr;
+    fhe_ring* ring = nullptr;
+    std::vector<uint64_t> c;
+    void* d_k = nullptr;
+};
+
+extern "C" int fhe_tower_scale_destroy(fhe_tower_scale* p) {
+    if (!p) return FHE_OK;
+    cudaSetDevice(p->ctx->device);
+    cudaDeviceSynchronize();
+    if (p->d_k) p->ctx->arena.release(p->d_k);
+    delete p;
+    return FHE_OK;
+}
+
+extern "C" int fhe_tower_scale_create(fhe_ring* ring, const uint64_t* c, fhe_tower_scale** out) {
+    if (!ring || !c || !out) return fail(FHE_EINVAL, "fhe_tower_scale_create: null argument");
+    *out = nullptr;
+    CUDA_TRY(cudaSetDevice(ring->ctx->device));
+    const uint32_t T = ring->dev.T;
+    std::vector<ulonglong4> k(T);
+    for (uint32_t i = 0; i < T; i++) {
+        const uint64_t qi = ring->q[i];
+        if (c[i] >= qi) return fail(FHE_EINVAL, "fhe_tower_scale_create: constant %u is not reduced modulo its tower", i);
+        k[i] = make_ulonglong4(c[i], host::shoup_companion(c[i], qi), host::shoup_companion(1, qi), 0);
+    }
+    auto* p = new fhe_tower_scale;
+    p->ctx = ring->ctx; p->ring = ring;
+    p->c.assign(c, c + T);
+    int rc = upload(p->ctx, k, &p->d_k);
+    if (rc) { fhe_tower_scale_destroy(p); return rc; }
+    *out = p;
+    return FHE_OK;
+}
+
+static int tower_scale_run(fhe_tower_scale* p, int mode, uint32_t sl, fhe_dptr dst, fhe_dptr src, size_t batch, int stream,
+                           const char* who) {
+    if (!p) return fail(FHE_EINVAL, "null tower-scale plan");
+    cudaStream_t s;
+    int rc = ring_stream(p->ring, stream, &s);
+    if (rc) return rc;
+    const uint32_t T = p->ring->dev.T;
+    if (mode == 0 && (sl == 0 || sl > T)) return fail(FHE_EINVAL, "%s: size_ql must be in [1, %u]", who, T);
+    if (batch == 0) return FHE_OK;
+    if (!dst || !src) return fail(FHE_EINVAL, "%s: null device pointer", who);
+    if (dst == src) return fail(FHE_EINVAL, "%s: dst must not be src (different tower counts)", who);
+    CUDA_TRY(launch_tower_scale(mode, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, batch, p->ring->dev.logN, sl, T,
+                                p->ring->dev.mods, (const ulonglong4*)p->d_k, s));
+    return FHE_OK;
+}
+
+extern "C" int fhe_expand_crt_basis_ql_hat(fhe_tower_scale* p, uint32_t size_ql, fhe_dptr dst_q, fhe_dptr src_ql, size_t batch,
+                                           int stream) {
+    return tower_scale_run(p, 0, size_ql, dst_q, src_ql, batch, stream, "fhe_expand_crt_basis_ql_hat");
+}
+extern "C" int fhe_scale_and_round_p_over_q(fhe_tower_scale* p, fhe_dptr dst_q, fhe_dptr src_qp, size_t batch, int stream) {
+    return tower_scale_run(p, 1, 0, dst_q, src_qp, batch, stream, "fhe_scale_and_round_p_over_q");
 }
 
 struct fhe_scale_round {

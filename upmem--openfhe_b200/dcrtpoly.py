@@ -370,6 +370,15 @@ class Basis:
         """self = Q -> P.  DCRTPolyImpl::ExpandCRTBasis (dcrtpoly-impl.h:1311-1358)."""
         N.check(N.lib.fhe_expand_crt_basis(self.h, dst_qp, src_q, batch, fmt, result_fmt, stream))
 
+    def expand_crt_basis_reverse_order(self, dst_pq, src_q, batch, fmt, result_fmt, stream=0):
+        """self = Q -> P.  DCRTPolyImpl::ExpandCRTBasisReverseOrder (dcrtpoly-impl.h:1361-1410): P towers first."""
+        N.check(N.lib.fhe_expand_crt_basis_reverse_order(self.h, dst_pq, src_q, batch, fmt, result_fmt, stream))
+
+    def fast_expand_crt_basis_pl_over_q(self, pl_to_ql, dst_qlpl, src_q, batch, stream=0):
+        """self = Q -> Pl built with the scheme's tables m_negRlQHatInvModq / m_qInvModr, pl_to_ql the exact switch back.
+        DCRTPolyImpl::FastExpandCRTBasisPloverQ (dcrtpoly-impl.h:1413-1468)."""
+        N.check(N.lib.fhe_fast_expand_crt_basis_pl_over_q(self.h, pl_to_ql.h, dst_qlpl, src_q, batch, stream))
+
     def approx_mod_up(self, dst_qp, src_q, batch, fmt, stream=0):
         """self = Q -> P.  DCRTPolyImpl::ApproxModUp (dcrtpoly-impl.h:1085-1133)."""
         N.check(N.lib.fhe_approx_mod_up(self.h, dst_qp, src_q, batch, fmt, stream))
@@ -377,6 +386,31 @@ class Basis:
     def approx_mod_down(self, dst_q, src_qp, batch, t=0, stream=0):
         """self = P -> Q.  DCRTPolyImpl::ApproxModDown (dcrtpoly-impl.h:1136-1175)."""
         N.check(N.lib.fhe_approx_mod_down(self.h, dst_q, src_qp, batch, t, stream))
+
+
+class TowerScale:
+    """One constant per tower of `ring`: DCRTPolyImpl::ExpandCRTBasisQlHat (dcrtpoly-impl.h:1514-1534, c = m_QlHatModq[l])
+    and DCRTPolyImpl::ScaleAndRoundPOverQ (dcrtpoly-impl.h:2052-2066, c = pInvModq)."""
+
+    def __init__(self, ring, c):
+        self.ring = ring
+        c = np.ascontiguousarray(c, np.uint64)
+        if c.size != ring.towers:
+            raise ValueError("one constant per tower")
+        h = ctypes.c_void_p()
+        N.check(N.lib.fhe_tower_scale_create(ring.h, c.ctypes.data, ctypes.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_tower_scale_destroy(self.h)
+            self.h = None
+
+    def expand_crt_basis_ql_hat(self, dst_q, src_ql, size_ql, batch, stream=0):
+        N.check(N.lib.fhe_expand_crt_basis_ql_hat(self.h, size_ql, dst_q, src_ql, batch, stream))
+
+    def scale_and_round_p_over_q(self, dst_q, src_qp, batch, stream=0):
+        N.check(N.lib.fhe_scale_and_round_p_over_q(self.h, dst_q, src_qp, batch, stream))
 
 
 class ScaleRound:
