@@ -516,6 +516,20 @@ def ntt_extra(pkg, be):
             "ms": ms, "ciphertext_products_per_s": batch / (ms * 1e-3),
             "note": "ExpandCRTBasis x4 -> tensor product over QR -> INTT -> ScaleAndRound -> SwitchCRTBasis, device-resident"}
         mult.close()
+        ring.close()
+        # the same product with the HPSPOVERQ technique (bfvrns-leveledshe.cpp:208-235, 357-366): R = 16 towers;
+        # a: 2 ExpandCRTBasis, b: 2 x (INTT, FastExpandCRTBasisPloverQ, NTT), tensor product, 3 x (INTT, ScaleAndRound to Q)
+        q, psi = pkg.gen_params(60, n, 2 * sq)
+        ring = pkg.Ring(be, n, q, psi)
+        neg, qinv = pkg.hps_p_over_q_tables(q[:sq], q[sq:])
+        frac, modq = pkg.hps_scale_tables(q[sq:], q[:sq], 65537)
+        mult = pkg.BfvHpsPOverQMult(ring, sq, neg, qinv, frac, modq)
+        ms = timed(lambda: mult(outs, ins[0:2], ins[2:4], batch), reps=3)
+        out["bfv_hpspoverq_evalmult_core_n32768_q16_r16_b32"] = {
+            "ms": ms, "ciphertext_products_per_s": batch / (ms * 1e-3),
+            "note": "ExpandCRTBasis x2 + (INTT, FastExpandCRTBasisPloverQ, NTT) x2 -> tensor product over QR -> INTT -> "
+                    "ScaleAndRound to Q, device-resident"}
+        mult.close()
         for p_ in ins + outs:
             be.free(p_)
         ring.close()

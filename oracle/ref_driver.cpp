@@ -682,6 +682,59 @@ static int bfv_hps_mult_impl(const ref_polys* a0, const ref_polys* a1, const ref
     return rc;
 }
 
+// The RNS core of BFVrns EvalMult with multTech == HPSPOVERQ (bfvrns-leveledshe.cpp:208-235, 322-334, 357-366) on the
+// reference's own DCRTPoly: cv1 ExpandCRTBasis Q -> QR, cv2 SetFormat(COEFFICIENT) + FastExpandCRTBasisPloverQ +
+// SetFormat(EVALUATION), the 2 x 2 tensor product, SetFormat(COEFFICIENT), ScaleAndRound QR -> Q with the t*Q/(QR)
+// tables (bfvrns-cryptoparameters.cpp:531-557; the same recipe as make_scale_tables with Q and R exchanged).
+// sizeR must equal sizeQ (FastExpandCRTBasisPloverQ: sizeQl = sizePl).  out[0..2] over Q in COEFFICIENT.
+int ref_bfv_hps_p_over_q_mult(const ref_polys* a0, const ref_polys* a1, const ref_polys* b0, const ref_polys* b1, ref_ctx* R,
+                              ref_ctx* QR, uint64_t t, ref_polys** out) {
+    int rc = 0;
+    std::string err;
+    serial_omp([&] {
+        try {
+            ref_ctx* Q = a0->ctx;
+            auto mq = moduli_of(Q), mr = moduli_of(R);
+            auto ex   = make_exact_tables(mq, mr);        // Q -> R
+            auto back = make_exact_tables(mr, mq);        // R -> Q
+            std::vector<NativeInteger> neg, negPrecon;
+            std::vector<std::vector<NativeInteger>> qInvModr;
+            make_pl_over_q_tables(mq, mr, neg, negPrecon, qInvModr);
+            DCRTPoly::CRTBasisExtensionPrecomputations basisPQ(QR->params, R->params, Q->params, neg, negPrecon, qInvModr, ex.sw.mu,
+                                                               back.sw.hatInv, back.sw.hatInvPrecon, back.hatModpT,
+                                                               back.alphaQModp, back.sw.mu, back.qInv);
+            std::vector<double> frac;
+            std::vector<std::vector<NativeInteger>> modq;
+            make_scale_tables(mr, mq, t, frac, modq);     // frac [sizeR], modq [sizeQ][sizeR+1]
+            for (int k = 0; k < 3; k++) out[k] = new ref_polys{Q, {}};
+            for (size_t i = 0; i < a0->v.size(); i++) {
+                DCRTPoly cv1[2] = {a0->v[i], a1->v[i]}, cv2[2] = {b0->v[i], b1->v[i]};
+                for (int k = 0; k < 2; k++) {
+                    cv1[k].ExpandCRTBasis(QR->params, R->params, ex.sw.hatInv, ex.sw.hatInvPrecon, ex.hatModpT, ex.alphaQModp,
+                                          ex.sw.mu, ex.qInv, Format::EVALUATION);
+                    cv2[k].SetFormat(Format::COEFFICIENT);
+                    cv2[k].FastExpandCRTBasisPloverQ(basisPQ);
+                    cv2[k].SetFormat(Format::EVALUATION);
+                }
+                DCRTPoly cvMult[3];
+                bool first[3] = {true, true, true};
+                for (int x = 0; x < 2; x++)
+                    for (int y = 0; y < 2; y++) {
+                        if (first[x + y]) { cvMult[x + y] = cv1[x] * cv2[y]; first[x + y] = false; }
+                        else cvMult[x + y] += cv1[x] * cv2[y];
+                    }
+                for (int k = 0; k < 3; k++) {
+                    cvMult[k].SetFormat(Format::COEFFICIENT);
+                    out[k]->v.push_back(cvMult[k].ScaleAndRound(Q->params, modq, frac, back.sw.mu));
+                }
+            }
+        }
+        catch (const std::exception& e) { err = e.what(); rc = 1; }
+    });
+    if (rc) g_ref_err = err;
+    return rc;
+}
+
 // mod-ops of the PimData surface executed by the reference's own NativeVector (in-place forms:
 // mubintvecnat.cpp:111-195,370-487, mubintvecnat.h:560-566).  kind = enum mod_kernel.
 // Returns 0, or 1 if the reference threw.

@@ -33,6 +33,47 @@ def constants(O, q, seed):
     return O.fill_ring(1, 1, np.ascontiguousarray(q, np.uint64), seed).reshape(-1).copy()
 
 
+MULT_CASES = [  # nbits, N, sizeQ (= sizeR), batch, seed, t
+    (30, 16, 2, 2, 20264001, 65537),
+    (60, 1 << 10, 3, 2, 20264002, 65537),
+    (60, 1 << 13, 5, 1, 20264003, 786433),
+]
+
+
+def mult_section(R, O, p):
+    """Section "bfv_p_over_q_mult": the RNS core of BFVrns EvalMult with multTech == HPSPOVERQ run by the reference's own
+    DCRTPoly (oracle/ref_driver.cpp: ref_bfv_hps_p_over_q_mult); the ScaleAndRound tables are stored for the GPU box."""
+    R.ref_scale_tables_get.argtypes = [vp, vp, u64, vp, vp]
+    R.ref_bfv_hps_p_over_q_mult.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp)]
+    out = []
+    for nbits, n, sq, batch, seed, t in MULT_CASES:
+        q, psi = np.zeros(2 * sq, np.uint64), np.zeros(2 * sq, np.uint64)
+        R.ref_gen_params(nbits, n, 2 * sq, p(q), p(psi))
+        mk = lambda a, b: R.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+        cQ, cR, cQR = mk(0, sq), mk(sq, 2 * sq), mk(0, 2 * sq)
+        frac, modq = np.empty(sq, np.float64), np.empty((sq, sq + 1), np.uint64)
+        R.ref_scale_tables_get(cR, cQ, t, p(frac), p(modq))
+        ins = [O.fill_ring(batch, n, q[:sq].copy(), seed + k) for k in range(4)]
+        hs = [R.ref_polys_load(cQ, p(v), batch, 0) for v in ins]
+        outs = (vp * 3)()
+        assert R.ref_bfv_hps_p_over_q_mult(hs[0], hs[1], hs[2], hs[3], cR, cQR, t, outs) == 0
+        rec = {"nbits": nbits, "N": n, "sizeQ": sq, "batch": batch, "seed": seed, "t": t, "q": [int(v) for v in q],
+               "psi": [int(v) for v in psi], "frac_hex": [float(v).hex() for v in frac],
+               "modq": [int(v) for v in modq.reshape(-1)], "sha_in": [digest(v) for v in ins], "sha_out": []}
+        for k in range(3):
+            res = np.empty((batch, sq, n), np.uint64)
+            R.ref_polys_store(outs[k], p(res))
+            rec["sha_out"].append(digest(res))
+            R.ref_polys_free(outs[k])
+        for h in hs:
+            R.ref_polys_free(h)
+        for c in (cQ, cR, cQR):
+            R.ref_ctx_destroy(c)
+        out.append(rec)
+        print("p-over-q mult case", n, sq, "done")
+    return out
+
+
 def main():
     R = ctypes.CDLL(oracle_py.REF_SO)
     R.ref_gen_params.argtypes = [u32, u32, u32, vp, vp]
@@ -112,6 +153,7 @@ def main():
     with open(path) as f:
         doc = json.load(f)
     doc["bfv_p_over_q"] = out
+    doc["bfv_p_over_q_mult"] = mult_section(R, O, p)
     doc["bfv_p_over_q_generator"] = "tests/golden/make_golden_poverq.py over oracle/_ref/libopenfhe_ref.so (reference commit e70da11)"
     with open(path, "w") as f:
         json.dump(doc, f, indent=1)

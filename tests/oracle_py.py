@@ -247,6 +247,20 @@ def _bfv_hps_mult(self, a0, a1, b0, b1, frac, modr):
     return out
 
 
+def _bfv_hps_p_over_q_mult(self, a0, a1, b0, b1, frac, modq):
+    """RNS core of BFVrns EvalMult (HPSPOVERQ), bfvrns-leveledshe.cpp:208-235, 322-334, 357-366: inputs over Q in
+    EVALUATION -> three polynomials over Q in COEFFICIENT.  frac [sizeR], modq [sizeQ][sizeR+1]: t*Q/(QR)."""
+    QP = self.o.ctx(self.n, self.q, self.psi)
+    q, r = self.q[:self.sq].copy(), self.q[self.sq:].copy()
+    e1 = [self.expand(v, 0, 0) for v in (a0, a1)]
+    e2 = [QP.ntt(self.o.fast_expand_pl_over_q(self.Q.ntt(v, inverse=True), self.n, q, q, r)) for v in (b0, b1)]
+    c0 = QP.elementwise(2, e1[0], e2[0])
+    c1 = QP.elementwise(0, QP.elementwise(2, e1[0], e2[1]), QP.elementwise(2, e1[1], e2[0]))
+    c2 = QP.elementwise(2, e1[1], e2[1])
+    return [self.scale_and_round(QP.ntt(c, inverse=True), frac, modq, 0) for c in (c0, c1, c2)]
+
+
+OracleBasis.bfv_hps_p_over_q_mult = _bfv_hps_p_over_q_mult
 OracleBasis.bfv_hps_mult = _bfv_hps_mult
 
 

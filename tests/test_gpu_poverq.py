@@ -133,3 +133,34 @@ def test_tower_scale_edge_cases(pkg, backend, oracle):
     with pytest.raises(pkg.FheError):
         pkg.TowerScale(rq, q[:sq])                                       # constants must be reduced
     plan.close(); rq.close(); d.close(); ring.close()
+
+
+@pytest.mark.parametrize("case", EXT["bfv_p_over_q_mult"], ids=lambda c: f"N{c['N']}_Q{c['sizeQ']}")
+def test_bfv_hps_p_over_q_mult_reference_golden(pkg, backend, oracle, case):
+    """The RNS core of BFVrns EvalMult (HPSPOVERQ) composed on the device vs the reference's digests and the oracle; the
+    host table recipes (hps_p_over_q_tables, hps_scale_tables with Q and R exchanged) vs the reference's tables."""
+    n, sq, batch, t = case["N"], case["sizeQ"], case["batch"], case["t"]
+    q, psi = np.array(case["q"], np.uint64), np.array(case["psi"], np.uint64)
+    frac = np.array([float.fromhex(v) for v in case["frac_hex"]], np.float64)
+    modq = np.array(case["modq"], np.uint64).reshape(sq, sq + 1)
+    f2, m2 = pkg.hps_scale_tables(q[sq:], q[:sq], t)
+    assert np.array_equal(f2, frac) and np.array_equal(m2, modq)
+    neg, qinv = pkg.hps_p_over_q_tables(q[:sq], q[sq:])
+    oneg, oqinv = oracle.pl_over_q_tables(q[:sq].copy(), q[sq:].copy())
+    assert np.array_equal(neg, oneg) and np.array_equal(qinv, oqinv)
+    ring = pkg.Ring(backend, n, q, psi)
+    mult = pkg.BfvHpsPOverQMult(ring, sq, neg, qinv, frac, modq)
+    ins = [oracle.fill_ring(batch, n, q[:sq].copy(), case["seed"] + k) for k in range(4)]
+    assert [digest(v) for v in ins] == case["sha_in"]
+    d = Dev(backend)
+    din = [d.put(v) for v in ins]
+    dout = [d.new(batch * sq * n) for _ in range(3)]
+    mult(dout, din[0:2], din[2:4], batch)
+    got = [backend.d2h(o, batch * sq * n).reshape(batch, sq, n) for o in dout]
+    assert [digest(v) for v in got] == case["sha_out"]
+    want = oracle.basis(n, q, psi, sq).bfv_hps_p_over_q_mult(ins[0], ins[1], ins[2], ins[3], frac, modq)
+    for k in range(3):
+        assert np.array_equal(got[k], want[k]), f"c{k}"
+    for k in range(4):
+        assert np.array_equal(backend.d2h(din[k], ins[k].size).reshape(ins[k].shape), ins[k]), "input modified"
+    mult.close(); d.close(); ring.close()

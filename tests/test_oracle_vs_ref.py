@@ -53,6 +53,7 @@ def ref():
     R.ref_polys_fast_expand_pl_over_q.argtypes = [vp, vp, vp, vp]
     R.ref_polys_expand_ql_hat.argtypes = [vp, vp, vp]
     R.ref_polys_scale_round_p_over_q.argtypes = [vp, vp, vp]
+    R.ref_bfv_hps_p_over_q_mult.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp)]
     R.ref_bfv_hps_mult.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp)]
     return R
 
@@ -339,3 +340,31 @@ def test_hps_p_over_q_set_matches_reference(oracle, ref, nbits, n, sq, sl):
         ref.ref_ctx_destroy(cq); ref.ref_ctx_destroy(cf)
     for cc in (cQ, cQl, cPl, cQlPl):
         ref.ref_ctx_destroy(cc)
+
+
+@pytest.mark.parametrize("nbits,n,sq,t", [(30, 16, 2, 65537), (60, 256, 3, 65537), (60, 1 << 11, 4, 786433)])
+def test_bfv_hps_p_over_q_mult_core_matches_reference(oracle, ref, nbits, n, sq, t):
+    """The RNS core of BFVrns EvalMult (HPSPOVERQ), bfvrns-leveledshe.cpp:208-235, 322-334, 357-366, executed by the
+    reference's own DCRTPoly vs the composition of the restated pieces; the t*Q/(QR) tables are the reference's
+    recipe with Q and R exchanged."""
+    q, psi = oracle.gen_params(nbits, n, 2 * sq)
+    ob = oracle.basis(n, q, psi, sq)
+    mk = lambda a, b: ref.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+    cQ, cR, cQR = mk(0, sq), mk(sq, 2 * sq), mk(0, 2 * sq)
+    B = 2
+    ins = [oracle.fill_ring(B, n, q[:sq].copy(), 190 + k) for k in range(4)]
+    hs = [ref.ref_polys_load(cQ, p(v), B, 0) for v in ins]
+    outs = (vp * 3)()
+    assert ref.ref_bfv_hps_p_over_q_mult(hs[0], hs[1], hs[2], hs[3], cR, cQR, t, outs) == 0, ref.ref_last_error()
+    frac, modq = np.empty(sq, np.float64), np.empty((sq, sq + 1), np.uint64)
+    ref.ref_scale_tables_get(cR, cQ, t, p(frac), p(modq))
+    want = ob.bfv_hps_p_over_q_mult(ins[0], ins[1], ins[2], ins[3], frac, modq)
+    for k in range(3):
+        res = np.empty((B, sq, n), np.uint64)
+        ref.ref_polys_store(outs[k], p(res))
+        assert np.array_equal(res, want[k]), f"c{k}"
+        ref.ref_polys_free(outs[k])
+    for h in hs:
+        ref.ref_polys_free(h)
+    for c in (cQ, cR, cQR):
+        ref.ref_ctx_destroy(c)

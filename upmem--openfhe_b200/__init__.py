@@ -8,8 +8,8 @@ Importing fails if lib/libfhe_b200.so has not been built: there is no CPU fallba
 """
 from . import _native
 from ._native import FheError, LIB_PATH, OP_ADD, OP_MUL, OP_SUB, SIGNATURES
-from .dcrtpoly import (COEFFICIENT, EVALUATION, Backend, Basis, BfvHpsMult, DCRTPolyBatch, Rescale, Ring, RingView, ScaleRound, TowerScale,
-                       gen_params, hps_scale_tables)
+from .dcrtpoly import (COEFFICIENT, EVALUATION, Backend, Basis, BfvHpsMult, BfvHpsPOverQMult, DCRTPolyBatch, Rescale, Ring, RingView, ScaleRound, TowerScale,
+                       gen_params, hps_p_over_q_tables, hps_scale_tables)
 
-__all__ = ["Backend", "Ring", "RingView", "Basis", "Rescale", "ScaleRound", "TowerScale", "BfvHpsMult", "hps_scale_tables", "DCRTPolyBatch", "gen_params", "FheError", "EVALUATION", "COEFFICIENT",
+__all__ = ["Backend", "Ring", "RingView", "Basis", "Rescale", "ScaleRound", "TowerScale", "BfvHpsMult", "BfvHpsPOverQMult", "hps_scale_tables", "hps_p_over_q_tables", "DCRTPolyBatch", "gen_params", "FheError", "EVALUATION", "COEFFICIENT",
            "OP_ADD", "OP_SUB", "OP_MUL", "LIB_PATH", "SIGNATURES"]

@@ -78,6 +78,9 @@ class Backend:
         self.sync(stream)               # the host array only has to outlive this call
         return arr
 
+    def d2d(self, dst, src, nbytes, stream=0):
+        N.check(N.lib.fhe_d2d(self.h, dst, src, nbytes, stream))
+
     def d2h(self, dptr, nwords, stream=0, out=None):
         if out is None:
             out = np.empty(nwords, np.uint64)
@@ -506,6 +509,72 @@ class BfvHpsMult:
         self.bufs, self.batch = [], 0
         for o in (self.scale, self.q2r, self.r2q, self.rq, self.rr):
             o.close()
+
+
+class BfvHpsPOverQMult:
+    """The RNS core of BFVrns EvalMult with the HPSPOVERQ technique (bfvrns-leveledshe.cpp:208-235, 322-334, 357-366)
+    composed from the device calls: a -> ExpandCRTBasis Q -> QR; b -> inverse NTT, FastExpandCRTBasisPloverQ (b*R/Q over
+    [Q | R]), forward NTT; the fused 2 x 2 tensor product over QR; inverse NTT; ScaleAndRound QR -> Q.  `ring_qr` holds the
+    Q towers followed by as many R towers; neg / qinv_modr are m_negRlQHatInvModq / m_qInvModr
+    (bfvrns-cryptoparameters.cpp:501-523), frac / modq the t*Q/(QR) tables (:531-557) = hps_scale_tables(r, q, t).
+    Inputs: a = (a0, a1), b = (b0, b1) device addresses over Q in EVALUATION; outputs c = (c0, c1, c2) over Q in COEFFICIENT."""
+
+    def __init__(self, ring_qr, size_q, neg, qinv_modr, frac, modq):
+        if ring_qr.towers != 2 * size_q:
+            raise ValueError("HPSPOVERQ needs as many R towers as Q towers")
+        self.ring, self.sq = ring_qr, size_q
+        self.rq, self.rr = RingView(ring_qr, 0, size_q), RingView(ring_qr, size_q, size_q)
+        self.q2r, self.r2q = Basis(self.rq, self.rr), Basis(self.rr, self.rq)
+        self.q2r_over = Basis(self.rq, self.rr, neg, qinv_modr)
+        self.scale = ScaleRound(ring_qr, size_q, frac, modq, out_last=False)
+        self.batch, self.bufs = 0, []
+
+    def _reserve(self, batch):
+        if batch <= self.batch:
+            return
+        be = self.ring.be
+        for p in self.bufs:
+            be.free(p)
+        wqr = self.ring.words(batch) * 8
+        self.bufs = [be.alloc(wqr) for _ in range(7)] + [be.alloc(self.rq.words(batch) * 8)]
+        self.batch = batch
+
+    def __call__(self, c, a, b, batch, stream=0):
+        self._reserve(batch)
+        e, t, coef = self.bufs[0:4], self.bufs[4:7], self.bufs[7]
+        be = self.ring.be
+        for dst, src in zip(e[0:2], a):
+            self.q2r.expand_crt_basis(dst, src, batch, EVALUATION, EVALUATION, stream)
+        for dst, src in zip(e[2:4], b):
+            be.d2d(coef, src, self.rq.words(batch) * 8, stream)
+            self.rq.ntt(coef, batch, inverse=True, stream=stream)
+            self.q2r_over.fast_expand_crt_basis_pl_over_q(self.r2q, dst, coef, batch, stream)
+            self.ring.ntt(dst, batch, inverse=False, stream=stream)
+        self.ring.ct_multiply(t, e[0:2], e[2:4], batch, 0, stream)
+        for k in range(3):
+            self.ring.ntt(t[k], batch, inverse=True, stream=stream)
+            self.scale.scale_and_round(c[k], t[k], batch, stream)
+
+    def close(self):
+        for p in self.bufs:
+            self.ring.be.free(p)
+        self.bufs, self.batch = [], 0
+        for o in (self.scale, self.q2r, self.r2q, self.q2r_over, self.rq, self.rr):
+            o.close()
+
+
+def hps_p_over_q_tables(q, r):
+    """m_negRlQHatInvModq [sizeQ] = q_i - [R * (Q/q_i)^-1]_{q_i} and m_qInvModr [sizeQ][sizeR] = [q_i^-1]_{r_j}, as
+    src/pke/lib/scheme/bfvrns/bfvrns-cryptoparameters.cpp:501-523 computes them (BigInteger there, Python integers here)."""
+    q, r = [int(v) for v in q], [int(v) for v in r]
+    Q, R = 1, 1
+    for v in q:
+        Q *= v
+    for v in r:
+        R *= v
+    neg = np.array([qi - (R * pow(Q // qi, -1, qi)) % qi for qi in q], np.uint64)
+    qinv = np.array([[pow(qi, -1, rj) for rj in r] for qi in q], np.uint64)
+    return neg, qinv
 
 
 def hps_scale_tables(q, r, t):
