@@ -543,6 +543,67 @@ inline bool resident_expand(PimManager *pim, const Towers &a, std::shared_ptr<Re
   return true;
 }
 
+/* DCRTPolyImpl::FastExpandCRTBasisPloverQ (dcrtpoly-impl.h:1413-1468, BFV HPSPOVERQ / HPSPOVERQLEVELED): a over Q -> out
+ * over [Ql | Pl] (`out` = host shells of those towers), format unchanged.  The first basis carries the scheme's own
+ * mPlQHatInvModq / qInvModp (cached by the table's address and checked against a copy of its values); the exact switch
+ * back uses the tables derived from the moduli, checked against the caller's PlHatInvModp. */
+template <class Towers, class IntVec, class Rows>
+inline bool resident_fast_expand_pl_over_q(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
+                                           std::shared_ptr<Resident> &rout, const IntVec &mPlQHatInvModq, const Rows &qInvModp,
+                                           const IntVec &PlHatInvModp) {
+  const size_t sq = a.size(), spl = out.size() / 2, sql = out.size() - spl;
+  if (!pim || a.empty() || spl == 0 || sql != spl || mPlQHatInvModq.size() < sq || qInvModp.size() < sq) return false;
+  auto da = ensure_device(pim, a, ra);
+  auto r = new_resident(pim, out);
+  static std::mutex mu;
+  static std::map<PimRing *, std::pair<std::shared_ptr<PimRing>, std::shared_ptr<PimRing>>> views;
+  struct Entry {
+    CachedPlan<PimBasis> plan;
+    std::vector<uint64_t> neg;
+  };
+  static std::map<std::tuple<PimRing *, PimRing *, const void *>, Entry> cache;
+  std::shared_ptr<PimRing> rql, rpl;
+  Entry e;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = views.find(r->ring.get());
+    if (it == views.end())
+      it = views.emplace(r->ring.get(), std::make_pair(PimRing::View(r->ring, 0, (uint32_t)sql),
+                                                       PimRing::View(r->ring, (uint32_t)sql, (uint32_t)spl))).first;
+    rql = it->second.first;
+    rpl = it->second.second;
+    std::vector<uint64_t> neg(sq);
+    for (size_t i = 0; i < sq; i++) neg[i] = mPlQHatInvModq[i].ConvertToInt();
+    auto key = std::make_tuple(da->ring.get(), rpl.get(), (const void *)&mPlQHatInvModq[0]);
+    auto ce = cache.find(key);
+    if (ce == cache.end() || ce->second.neg != neg) {
+      std::vector<uint64_t> flat;
+      flat.reserve(sq * spl);
+      for (size_t i = 0; i < sq; i++) {
+        if (qInvModp[i].size() < spl) return false;
+        for (size_t j = 0; j < spl; j++) flat.push_back(qInvModp[i][j].ConvertToInt());
+      }
+      Entry fresh;
+      fresh.plan.plan = std::make_shared<PimBasis>(da->ring, rpl, neg, flat);
+      fresh.neg = neg;
+      cache[key] = fresh;
+      ce = cache.find(key);
+    }
+    e = ce->second;
+  }
+  auto back = basis_for(rpl, rql);
+  if (!same_hat_inv(back, PlHatInvModp, spl, sql)) return false;
+  {
+    std::lock_guard<std::mutex> l1(e.plan.lock->mu);
+    std::lock_guard<std::mutex> l2(back.lock->mu);
+    PimManager::check(fhe_fast_expand_crt_basis_pl_over_q(e.plan.plan->handle(), back.plan->handle(), r->d, da->d, 1, 0),
+                      "pim hook: fast expand P over Q");
+  }
+  finish(r->ctx);
+  rout = r;
+  return true;
+}
+
 /* DCRTPolyImpl::ScaleAndRound(paramsOutput, ...) (dcrtpoly-impl.h:1876-1960, BFV): a over QP -> out over the output
  * basis (its first towers, or its last when out_last).  The plan is built from the scheme's own tables and cached by
  * their address; a hit is checked against a copy of the fractions, so a table reallocated at the same address is caught. */

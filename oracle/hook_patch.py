@@ -285,6 +285,24 @@ def patch_impl(text):
                 "    }\n"
                 "    DCRTPolyImpl<VecType> ans(paramsOutput, m_format, true);\n"
                 "    usint ringDim      = m_params->GetRingDimension();\n", rel)
+    # FastExpandCRTBasisPloverQ (in place, Q -> QlPl, format unchanged; BFV HPSPOVERQ / HPSPOVERQLEVELED)
+    sig = ("void DCRTPolyImpl<VecType>::FastExpandCRTBasisPloverQ(const Precomputations& precomputed) {\n"
+           "    usint ringDim = m_params->GetRingDimension();\n")
+    text = once(text, sig,
+                "void DCRTPolyImpl<VecType>::FastExpandCRTBasisPloverQ(const Precomputations& precomputed) {\n"
+                "    if (pim && !m_vectors_.empty()) {\n"
+                "        std::vector<DCRTPolyImpl::PolyType> shell;\n"
+                "        for (const auto& tp : precomputed.paramsQlPl->GetParams()) shell.emplace_back(tp, m_format, false);\n"
+                "        std::shared_ptr<pimhook::Resident> up;\n"
+                "        if (pimhook::resident_fast_expand_pl_over_q(pim.get(), m_vectors_, pimres_, shell, up, precomputed.mPlQHatInvModq,\n"
+                "                                                    precomputed.qInvModp, precomputed.PlHatInvModp)) {\n"
+                "            m_vectors_ = std::move(shell);\n"
+                "            pimres_    = up;\n"
+                "            m_params   = precomputed.paramsQlPl;\n"
+                "            return;\n"
+                "        }\n"
+                "    }\n"
+                "    usint ringDim = m_params->GetRingDimension();\n", rel)
     # ApproxModDown (const, EVALUATION input over QP, returns a polynomial over Q)
     sig = ("    usint sizeQP = m_vectors.size();\n    usint sizeP  = paramsP->GetParams().size();\n    usint sizeQ  = sizeQP - sizeP;\n")
     text = once(text, sig,

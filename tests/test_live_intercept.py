@@ -352,6 +352,57 @@ def test_resident_bfv_evalmult_core(hooked, oracle, pkg):
 
 
 @pytest.mark.gpu
+def test_resident_bfv_hps_p_over_q_evalmult_core(hooked, oracle, pkg):
+    """The same with the HPSPOVERQ technique (bfvrns-leveledshe.cpp:208-235, 322-334, 357-366; the default of the reference's
+    BFV): ExpandCRTBasis x2, SetFormat + FastExpandCRTBasisPloverQ + SetFormat x2, Times / +=, SetFormat, ScaleAndRound to Q
+    on the reference's own DCRTPoly with the operands attached — all on the device, results equal to the CPU path."""
+    H = hooked
+    H.ref_bfv_hps_p_over_q_mult.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp)]
+    n, sq, batch, t = 1 << 11, 3, 2, 65537
+    q, psi = oracle.gen_params(60, n, 2 * sq)
+    mk = lambda a, b: H.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+    cQ, cR, cQR = mk(0, sq), mk(sq, 2 * sq), mk(0, 2 * sq)
+    data = [oracle.fill_ring(batch, n, q[:sq].copy(), 180 + k) for k in range(4)]
+
+    def run(attach):
+        hs = [H.ref_polys_load(cQ, p(d), batch, 0) for d in data]
+        if attach:
+            for h in hs:
+                assert H.ref_polys_set_pim(h, 1) == 0, H.ref_last_error()
+        outs = (vp * 3)()
+        c0 = counters(H)
+        assert H.ref_bfv_hps_p_over_q_mult(hs[0], hs[1], hs[2], hs[3], cR, cQR, t, outs) == 0, H.ref_last_error()
+        c1 = counters(H)
+        res = []
+        for k in range(3):
+            r = np.empty((batch, sq, n), np.uint64)
+            H.ref_polys_store(outs[k], p(r))
+            res.append(r)
+            H.ref_polys_free(outs[k])
+        c2 = counters(H)
+        for h in hs:
+            H.ref_polys_free(h)
+        return res, (c1[0] - c0[0], c1[1] - c0[1]), (c2[0] - c1[0], c2[1] - c1[1])
+
+    launches0 = pkg._native.lib.fhe_launch_count()
+    got, during, after = run(True)
+    assert pkg._native.lib.fhe_launch_count() - launches0 >= 20 * batch
+    assert during == (4 * batch, 0), during                 # operands go up once, nothing comes down during the product
+    assert after == (0, 3 * batch), after
+    want, cpu_during, _ = run(False)
+    assert cpu_during == (0, 0)
+    for k in range(3):
+        assert np.array_equal(got[k], want[k]), f"c{k}"
+    ob = oracle.basis(n, q, psi, sq)
+    frac, modq = pkg.hps_scale_tables(q[sq:], q[:sq], t)
+    orc = ob.bfv_hps_p_over_q_mult(data[0], data[1], data[2], data[3], frac, modq)
+    for k in range(3):
+        assert np.array_equal(got[k], orc[k]), f"oracle c{k}"
+    for c in (cQ, cR, cQR):
+        H.ref_ctx_destroy(c)
+
+
+@pytest.mark.gpu
 def test_resident_poly_serialises_through_the_reference(hooked, oracle, pkg):
     """Serial::Serialize of the reference (DCRTPolyImpl::save, dcrtpoly.h:349-354) reads the towers through the const
     accessor, so a device-resident result is downloaded once and written in the wire format; the stream equals the one
