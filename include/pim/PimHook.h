@@ -517,26 +517,31 @@ inline bool resident_switch_exact(PimManager *pim, const Towers &a, std::shared_
  * result_format; `out` = host shells of the QP towers */
 template <class Towers, class IntVec>
 inline bool resident_expand(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
-                            std::shared_ptr<Resident> &rout, int format, int result_format, const IntVec &QHatInvModq) {
+                            std::shared_ptr<Resident> &rout, int format, int result_format, const IntVec &QHatInvModq,
+                            bool reverse = false) {      /* reverse: ExpandCRTBasisReverseOrder (:1361-1410), P towers first */
   if (!pim || a.empty() || out.size() <= a.size()) return false;
   auto da = ensure_device(pim, a, ra);
   auto r = new_resident(pim, out);
   const size_t sq = a.size(), sp = out.size() - sq;
   static std::mutex mu;
-  static std::map<std::pair<PimRing *, size_t>, std::shared_ptr<PimRing>> views;
+  static std::map<std::tuple<PimRing *, size_t, bool>, std::shared_ptr<PimRing>> views;
   std::shared_ptr<PimRing> rp;
   {
     std::lock_guard<std::mutex> lock(mu);
-    auto key = std::make_pair(r->ring.get(), sq);
+    auto key = std::make_tuple(r->ring.get(), sq, reverse);
     auto it = views.find(key);
-    if (it == views.end()) it = views.emplace(key, PimRing::View(r->ring, (uint32_t)sq, (uint32_t)sp)).first;
+    if (it == views.end()) it = views.emplace(key, PimRing::View(r->ring, reverse ? 0u : (uint32_t)sq, (uint32_t)sp)).first;
     rp = it->second;
   }
   auto plan = basis_for(da->ring, rp);
   if (!same_hat_inv(plan, QHatInvModq, sq, sp)) return false;
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
-    PimManager::check(fhe_expand_crt_basis(plan.plan->handle(), r->d, da->d, 1, format, result_format, 0), "pim hook: expand basis");
+    if (reverse)
+      PimManager::check(fhe_expand_crt_basis_reverse_order(plan.plan->handle(), r->d, da->d, 1, format, result_format, 0),
+                        "pim hook: expand basis (reverse order)");
+    else
+      PimManager::check(fhe_expand_crt_basis(plan.plan->handle(), r->d, da->d, 1, format, result_format, 0), "pim hook: expand basis");
   }
   finish(r->ctx);
   rout = r;
@@ -600,6 +605,51 @@ inline bool resident_fast_expand_pl_over_q(PimManager *pim, const Towers &a, std
                       "pim hook: fast expand P over Q");
   }
   finish(r->ctx);
+  rout = r;
+  return true;
+}
+
+/* DCRTPolyImpl::ExpandCRTBasisQlHat (dcrtpoly-impl.h:1514-1534; mode 0: a over the first towers of `out`'s basis) and
+ * DCRTPolyImpl::ScaleAndRoundPOverQ (dcrtpoly-impl.h:2052-2066; mode 1: a over `out`'s basis plus one tower).  The plan is
+ * built from the caller's constants, cached by their address and checked against a copy of the values. */
+template <class Towers, class IntVec>
+inline bool resident_tower_scale(PimManager *pim, int mode, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
+                                 std::shared_ptr<Resident> &rout, const IntVec &c) {
+  const size_t T = out.size(), sl = mode == 0 ? a.size() : T;
+  if (!pim || a.empty() || T == 0 || c.size() < sl) return false;
+  if (mode == 0 ? a.size() > T : a.size() != T + 1) return false;
+  auto da = ensure_device(pim, a, ra);
+  auto r = new_resident(pim, out);
+  struct Entry {
+    CachedPlan<PimTowerScale> plan;
+    std::vector<uint64_t> c;
+  };
+  static std::mutex mu;
+  static std::map<std::tuple<PimRing *, const void *, size_t>, Entry> cache;
+  Entry e;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    std::vector<uint64_t> k(T, 0);
+    for (size_t i = 0; i < sl; i++) k[i] = c[i].ConvertToInt();
+    auto key = std::make_tuple(r->ring.get(), (const void *)&c[0], sl);
+    auto it = cache.find(key);
+    if (it == cache.end() || it->second.c != k) {
+      Entry fresh;
+      fresh.plan.plan = std::make_shared<PimTowerScale>(r->ring, k);
+      fresh.c = k;
+      cache[key] = fresh;
+      it = cache.find(key);
+    }
+    e = it->second;
+  }
+  {
+    std::lock_guard<std::mutex> lock(e.plan.lock->mu);
+    if (mode == 0)
+      PimManager::check(fhe_expand_crt_basis_ql_hat(e.plan.plan->handle(), (uint32_t)sl, r->d, da->d, 1, 0),
+                        "pim hook: expand basis (QlHat)");
+    else
+      PimManager::check(fhe_scale_and_round_p_over_q(e.plan.plan->handle(), r->d, da->d, 1, 0), "pim hook: scale and round P over Q");
+  }
   rout = r;
   return true;
 }

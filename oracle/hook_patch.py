@@ -303,6 +303,60 @@ def patch_impl(text):
                 "        }\n"
                 "    }\n"
                 "    usint ringDim = m_params->GetRingDimension();\n", rel)
+    # ExpandCRTBasisReverseOrder (in place, Q -> PQ)
+    start = text.index("void DCRTPolyImpl<VecType>::ExpandCRTBasisReverseOrder(\n")
+    sig = ("    const std::vector<DoubleNativeInt>& modpBarrettMu, const std::vector<double>& qInv, Format resultFormat) {\n"
+           "    std::vector<DCRTPolyImpl::PolyType> polyInNTT;\n")
+    at = text.index(sig, start)
+    text = text[:at] + text[at:].replace(sig,
+                "    const std::vector<DoubleNativeInt>& modpBarrettMu, const std::vector<double>& qInv, Format resultFormat) {\n"
+                "    if (pim && !m_vectors_.empty() && paramsQP->GetParams().size() == m_vectors_.size() + paramsP->GetParams().size()) {\n"
+                "        std::vector<DCRTPolyImpl::PolyType> shell;\n"
+                "        for (const auto& tp : paramsQP->GetParams()) shell.emplace_back(tp, resultFormat, false);\n"
+                "        std::shared_ptr<pimhook::Resident> up;\n"
+                "        if (pimhook::resident_expand(pim.get(), m_vectors_, pimres_, shell, up, m_format == Format::EVALUATION ? 0 : 1,\n"
+                "                                     resultFormat == Format::EVALUATION ? 0 : 1, QHatInvModq, true)) {\n"
+                "            m_vectors_ = std::move(shell);\n"
+                "            pimres_    = up;\n"
+                "            m_format   = resultFormat;\n"
+                "            m_params   = paramsQP;\n"
+                "            return;\n"
+                "        }\n"
+                "    }\n"
+                "    std::vector<DCRTPolyImpl::PolyType> polyInNTT;\n", 1)
+    # ExpandCRTBasisQlHat (in place, Ql -> Q) and ScaleAndRoundPOverQ (in place, Q plus one tower -> Q)
+    sig = ("                                                const std::vector<NativeInteger>& QlHatModqPrecon, const usint sizeQ) {\n"
+           "    size_t sizeQl(m_vectors.size());\n")
+    text = once(text, sig,
+                "                                                const std::vector<NativeInteger>& QlHatModqPrecon, const usint sizeQ) {\n"
+                "    if (pim && !m_vectors_.empty() && paramsQ->GetParams().size() == sizeQ) {\n"
+                "        std::vector<DCRTPolyImpl::PolyType> shell;\n"
+                "        for (const auto& tp : paramsQ->GetParams()) shell.emplace_back(tp, m_format, false);\n"
+                "        std::shared_ptr<pimhook::Resident> up;\n"
+                "        if (pimhook::resident_tower_scale(pim.get(), 0, m_vectors_, pimres_, shell, up, QlHatModq)) {\n"
+                "            m_vectors_ = std::move(shell);\n"
+                "            pimres_    = up;\n"
+                "            m_params   = paramsQ;\n"
+                "            return;\n"
+                "        }\n"
+                "    }\n"
+                "    size_t sizeQl(m_vectors.size());\n", rel)
+    sig = ("                                                const std::vector<NativeInteger>& pInvModq) {\n"
+           "    const usint sizeQ   = m_vectors.size() - 1;\n")
+    text = once(text, sig,
+                "                                                const std::vector<NativeInteger>& pInvModq) {\n"
+                "    if (pim && m_vectors_.size() == paramsQ->GetParams().size() + 1) {\n"
+                "        std::vector<DCRTPolyImpl::PolyType> shell;\n"
+                "        for (const auto& tp : paramsQ->GetParams()) shell.emplace_back(tp, m_format, false);\n"
+                "        std::shared_ptr<pimhook::Resident> up;\n"
+                "        if (pimhook::resident_tower_scale(pim.get(), 1, m_vectors_, pimres_, shell, up, pInvModq)) {\n"
+                "            m_vectors_ = std::move(shell);\n"
+                "            pimres_    = up;\n"
+                "            m_params   = paramsQ;\n"
+                "            return;\n"
+                "        }\n"
+                "    }\n"
+                "    const usint sizeQ   = m_vectors.size() - 1;\n", rel)
     # ApproxModDown (const, EVALUATION input over QP, returns a polynomial over Q)
     sig = ("    usint sizeQP = m_vectors.size();\n    usint sizeP  = paramsP->GetParams().size();\n    usint sizeQ  = sizeQP - sizeP;\n")
     text = once(text, sig,

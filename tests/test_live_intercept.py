@@ -403,6 +403,57 @@ def test_resident_bfv_hps_p_over_q_evalmult_core(hooked, oracle, pkg):
 
 
 @pytest.mark.gpu
+def test_resident_p_over_q_tails_and_reverse_expand(hooked, oracle, pkg):
+    """ExpandCRTBasisReverseOrder, ExpandCRTBasisQlHat and ScaleAndRoundPOverQ (dcrtpoly-impl.h:1361-1410, 1514-1534,
+    2052-2066) of the reference's own DCRTPoly with the handle attached: one upload, no download until the result is read,
+    values equal to the CPU path and the oracle."""
+    H = hooked
+    H.ref_polys_expand_crt_basis_reverse.argtypes = [vp, vp, vp, ci]
+    H.ref_polys_expand_ql_hat.argtypes = [vp, vp, vp]
+    H.ref_polys_scale_round_p_over_q.argtypes = [vp, vp, vp]
+    n, sq, sp, batch = 1 << 11, 3, 2, 2
+    q, psi = oracle.gen_params(60, n, sq + sp)
+    mk = lambda qq, pp: H.ref_ctx_create(n, len(qq), p(np.ascontiguousarray(qq, np.uint64)), p(np.ascontiguousarray(pp, np.uint64)))
+    cQ, cP, cQP = mk(q[:sq], psi[:sq]), mk(q[sq:], psi[sq:]), mk(q, psi)
+    cPQ = mk(np.concatenate([q[sq:], q[:sq]]), np.concatenate([psi[sq:], psi[:sq]]))
+    cQ1 = mk(q[:sq + 1], psi[:sq + 1])
+    x = oracle.fill_ring(batch, n, q[:sq].copy(), 301)
+    z = oracle.fill_ring(batch, n, q[:sq + 1].copy(), 302)
+    k = oracle.fill_ring(1, 1, q.copy(), 303).reshape(-1).copy()
+    ob = oracle.basis(n, q, psi, sq)
+
+    def run(attach, src, ctx, fmt, call, towers):
+        h = H.ref_polys_load(ctx, p(src), batch, fmt)
+        if attach:
+            assert H.ref_polys_set_pim(h, 1) == 0, H.ref_last_error()
+        c0 = counters(H)
+        assert call(h) == 0, H.ref_last_error()
+        c1 = counters(H)
+        res = np.empty((batch, towers, n), np.uint64)
+        H.ref_polys_store(h, p(res))
+        H.ref_polys_free(h)
+        return res, (c1[0] - c0[0], c1[1] - c0[1])
+
+    cases = [
+        ("reverse f0->r0", x, cQ, 0, lambda h: H.ref_polys_expand_crt_basis_reverse(h, cP, cPQ, 0), sq + sp, lambda: ob.expand_reverse(x, 0, 0)),
+        ("reverse f1->r0", x, cQ, 1, lambda h: H.ref_polys_expand_crt_basis_reverse(h, cP, cPQ, 0), sq + sp, lambda: ob.expand_reverse(x, 1, 0)),
+        ("reverse f0->r1", x, cQ, 0, lambda h: H.ref_polys_expand_crt_basis_reverse(h, cP, cPQ, 1), sq + sp, lambda: ob.expand_reverse(x, 0, 1)),
+        ("ql hat", x, cQ, 0, lambda h: H.ref_polys_expand_ql_hat(h, cQP, p(k)), sq + sp, lambda: oracle.expand_ql_hat(x, n, q, sq, k[:sq])),
+        ("p over q", z, cQ1, 1, lambda h: H.ref_polys_scale_round_p_over_q(h, cQ, p(k)), sq,
+         lambda: oracle.scale_round_p_over_q(z, n, q[:sq].copy(), k[:sq])),
+    ]
+    for name, src, ctx, fmt, call, towers, want in cases:
+        got, moved = run(True, src, ctx, fmt, call, towers)
+        assert moved == (batch, 0), (name, moved)
+        cpu, cpu_moved = run(False, src, ctx, fmt, call, towers)
+        assert cpu_moved == (0, 0), name
+        assert np.array_equal(got, cpu), name
+        assert np.array_equal(got, want()), name + " vs oracle"
+    for c in (cQ, cP, cQP, cPQ, cQ1):
+        H.ref_ctx_destroy(c)
+
+
+@pytest.mark.gpu
 def test_resident_poly_serialises_through_the_reference(hooked, oracle, pkg):
     """Serial::Serialize of the reference (DCRTPolyImpl::save, dcrtpoly.h:349-354) reads the towers through the const
     accessor, so a device-resident result is downloaded once and written in the wire format; the stream equals the one
