@@ -494,6 +494,18 @@ def ntt_extra(pkg, be):
         out["approx_mod_down_n65536_q30_p10_b16"] = {"ms": ms, "polys_per_s": batch / (ms * 1e-3)}
         ms = timed(lambda: plan.drop_last_element_and_scale(dr, dqp, batch, 0))
         out["drop_last_element_and_scale_n65536_t40_b16"] = {"ms": ms, "polys_per_s": batch / (ms * 1e-3)}
+        # HPSPOVERQ tails (tower_scale_kernel): HBM-bound, 8 B in + 8 B out per coefficient per tower (+ the extra tower)
+        rq1 = pkg.RingView(ring, 0, sq + sp - 1)
+        kq = [int(v) // 3 for v in q[:sq + sp - 1]]
+        ts = pkg.TowerScale(rq1, kq)
+        ms = timed(lambda: ts.scale_and_round_p_over_q(dr, dqp, batch))
+        out["scale_and_round_p_over_q_n65536_t39_b16"] = {
+            "ms": ms, "polys_per_s": batch / (ms * 1e-3), "hbm_gbs": batch * n * (2 * (sq + sp) - 1) * 8 / (ms * 1e-3) / 1e9}
+        ms = timed(lambda: ts.expand_crt_basis_ql_hat(dr, dq, sq, batch))
+        out["expand_crt_basis_ql_hat_n65536_l30_t39_b16"] = {
+            "ms": ms, "polys_per_s": batch / (ms * 1e-3), "hbm_gbs": batch * n * (sq + sq + sp - 1) * 8 / (ms * 1e-3) / 1e9}
+        ts.close()
+        rq1.close()
         for o in (q2p, p2q, plan, rq, rp):
             o.close()
         for b_ in (dq, dp, dqp, dr):

@@ -687,11 +687,15 @@ static int bfv_hps_mult_impl(const ref_polys* a0, const ref_polys* a1, const ref
 // SetFormat(EVALUATION), the 2 x 2 tensor product, SetFormat(COEFFICIENT), ScaleAndRound QR -> Q with the t*Q/(QR)
 // tables (bfvrns-cryptoparameters.cpp:531-557; the same recipe as make_scale_tables with Q and R exchanged).
 // sizeR must equal sizeQ (FastExpandCRTBasisPloverQ: sizeQl = sizePl).  out[0..2] over Q in COEFFICIENT.
-int ref_bfv_hps_p_over_q_mult(const ref_polys* a0, const ref_polys* a1, const ref_polys* b0, const ref_polys* b1, ref_ctx* R,
-                              ref_ctx* QR, uint64_t t, ref_polys** out) {
+static int bfv_hps_p_over_q_mult_impl(const ref_polys* a0, const ref_polys* a1, const ref_polys* b0, const ref_polys* b1, ref_ctx* R,
+                                      ref_ctx* QR, uint64_t t, ref_polys** out, int outer_threads, double* seconds) {
     int rc = 0;
     std::string err;
-    serial_omp([&] {
+    auto run = [&](auto body) {
+        if (outer_threads > 1) body();
+        else serial_omp(body);
+    };
+    run([&] {
         try {
             ref_ctx* Q = a0->ctx;
             auto mq = moduli_of(Q), mr = moduli_of(R);
@@ -706,8 +710,13 @@ int ref_bfv_hps_p_over_q_mult(const ref_polys* a0, const ref_polys* a1, const re
             std::vector<double> frac;
             std::vector<std::vector<NativeInteger>> modq;
             make_scale_tables(mr, mq, t, frac, modq);     // frac [sizeR], modq [sizeQ][sizeR+1]
-            for (int k = 0; k < 3; k++) out[k] = new ref_polys{Q, {}};
-            for (size_t i = 0; i < a0->v.size(); i++) {
+            for (int k = 0; k < 3; k++) {
+                out[k] = new ref_polys{Q, {}};
+                out[k]->v.resize(a0->v.size());
+            }
+            auto t0 = std::chrono::steady_clock::now();
+#pragma omp parallel for num_threads(outer_threads) schedule(dynamic) if (outer_threads > 1)
+            for (long i = 0; i < (long)a0->v.size(); i++) {
                 DCRTPoly cv1[2] = {a0->v[i], a1->v[i]}, cv2[2] = {b0->v[i], b1->v[i]};
                 for (int k = 0; k < 2; k++) {
                     cv1[k].ExpandCRTBasis(QR->params, R->params, ex.sw.hatInv, ex.sw.hatInvPrecon, ex.hatModpT, ex.alphaQModp,
@@ -725,14 +734,27 @@ int ref_bfv_hps_p_over_q_mult(const ref_polys* a0, const ref_polys* a1, const re
                     }
                 for (int k = 0; k < 3; k++) {
                     cvMult[k].SetFormat(Format::COEFFICIENT);
-                    out[k]->v.push_back(cvMult[k].ScaleAndRound(Q->params, modq, frac, back.sw.mu));
+                    out[k]->v[i] = cvMult[k].ScaleAndRound(Q->params, modq, frac, back.sw.mu);
                 }
             }
+            if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         }
         catch (const std::exception& e) { err = e.what(); rc = 1; }
     });
     if (rc) g_ref_err = err;
     return rc;
+}
+int ref_bfv_hps_p_over_q_mult(const ref_polys* a0, const ref_polys* a1, const ref_polys* b0, const ref_polys* b1, ref_ctx* R,
+                              ref_ctx* QR, uint64_t t, ref_polys** out) {
+    return bfv_hps_p_over_q_mult_impl(a0, a1, b0, b1, R, QR, t, out, 1, nullptr);
+}
+// timed form, as ref_bfv_hps_mult_timed
+int ref_bfv_hps_p_over_q_mult_timed(const ref_polys* a0, const ref_polys* a1, const ref_polys* b0, const ref_polys* b1, ref_ctx* R,
+                                    ref_ctx* QR, uint64_t t, ref_polys** out, int outer_threads, double* seconds) {
+#ifndef FHE_HOOKED
+    outer_threads = 1;
+#endif
+    return bfv_hps_p_over_q_mult_impl(a0, a1, b0, b1, R, QR, t, out, outer_threads, seconds);
 }
 
 // mod-ops of the PimData surface executed by the reference's own NativeVector (in-place forms:

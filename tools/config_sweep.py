@@ -154,6 +154,25 @@ def main():
     mult.close()
     rq.close()
     ring.close()
+    # the same product with the reference's default BFV technique, HPSPOVERQ (R = 16 towers)
+    q2, psi2 = pkg.gen_params(60, n, 2 * sq)
+    ring = pkg.Ring(be, n, q2, psi2)
+    rq = pkg.RingView(ring, 0, sq)
+    neg, qinv = pkg.hps_p_over_q_tables(q2[:sq], q2[sq:])
+    frac2, modq2 = pkg.hps_scale_tables(q2[sq:], q2[:sq], t)
+    mult = pkg.BfvHpsPOverQMult(ring, sq, neg, qinv, frac2, modq2)
+
+    def mk_cfg4c(chunk):
+        w = rq.words(chunk) * 8
+        bufs = [be.alloc(w) for _ in range(7)]
+        for i in range(4):
+            rq.fill_uniform(bufs[i], chunk, 990 + i + 17 * rank)
+        return (lambda c: mult(bufs[4:7], bufs[0:2], bufs[2:4], c)), (lambda: [be.free(b) for b in bufs])
+
+    run("cfg4_bfv_hpspoverq_evalmult_core_n32768_q16_r16", n, 2 * sq, mk_cfg4c, None)
+    mult.close()
+    rq.close()
+    ring.close()
     be.close()
     if rank == 0:
         if args.cpu_sample > 0:

@@ -4,7 +4,9 @@ ScaleAndRound, SwitchCRTBasis), N = 2^15, 16 + 17 towers.
   cpu   the hooked build's CPU path, one ciphertext pair per host thread (all threads)
   b200  the same code with the operands attached (SetPim): one launch sequence per pair, operands uploaded once,
         the three result polys downloaded (ref_polys_store) inside the timed region
-Usage: python tools/hook_bfv_bench.py [pairs]   ->  one JSON line"""
+Usage: python tools/hook_bfv_bench.py [pairs] [hps|hpspoverq]   ->  one JSON line
+hpspoverq: the reference's default BFV technique (bfv_hps_p_over_q_mult_impl: ExpandCRTBasis x2, SetFormat +
+FastExpandCRTBasisPloverQ + SetFormat x2, Times / +=, SetFormat, ScaleAndRound to Q), 16 + 16 towers."""
 import ctypes
 import json
 import os
@@ -17,7 +19,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from tests import oracle_py  # noqa: E402
 
 pairs = int(sys.argv[1]) if len(sys.argv) > 1 else 16
-n, sq, sr, t = 1 << 15, 16, 17, 65537
+tech = sys.argv[2] if len(sys.argv) > 2 else "hps"
+n, sq, sr, t = 1 << 15, 16, (17 if tech == "hps" else 16), 65537
 vp, sz, ci, u32, u64 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint32, ctypes.c_uint64
 H = ctypes.CDLL(os.path.join(os.path.dirname(oracle_py.REF_SO), "libopenfhe_hooked.so"))
 H.ref_ctx_create.restype = vp; H.ref_ctx_create.argtypes = [u32, u32, vp, vp]
@@ -26,14 +29,15 @@ H.ref_polys_store.argtypes = [vp, vp]; H.ref_polys_free.argtypes = [vp]
 H.ref_polys_set_pim.argtypes = [vp, ci]
 H.ref_max_threads.restype = ci
 H.ref_last_error.restype = ctypes.c_char_p
-H.ref_bfv_hps_mult_timed.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp), ci, ctypes.POINTER(ctypes.c_double)]
+mult_timed = H.ref_bfv_hps_mult_timed if tech == "hps" else H.ref_bfv_hps_p_over_q_mult_timed
+mult_timed.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp), ci, ctypes.POINTER(ctypes.c_double)]
 p = lambda a: a.ctypes.data_as(vp)
 O = oracle_py.load()
 q, psi = O.gen_params(60, n, sq + sr)
 mk = lambda a, b: H.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
 cQ, cR, cQR = mk(0, sq), mk(sq, sq + sr), mk(0, sq + sr)
 data = [O.fill_ring(pairs, n, q[:sq].copy(), 700 + k) for k in range(4)]
-out, results = {"N": n, "towers_q": sq, "towers_r": sr, "pairs": pairs}, {}
+out, results = {"technique": tech, "N": n, "towers_q": sq, "towers_r": sr, "pairs": pairs}, {}
 for mode in ("cpu", "b200"):
     threads = H.ref_max_threads() if mode == "cpu" else 1
     best = None
@@ -45,7 +49,7 @@ for mode in ("cpu", "b200"):
         outs, sec = (vp * 3)(), ctypes.c_double()
         res = [np.empty((pairs, sq, n), np.uint64) for _ in range(3)]
         t0 = time.perf_counter()
-        assert H.ref_bfv_hps_mult_timed(hs[0], hs[1], hs[2], hs[3], cR, cQR, t, outs, threads, ctypes.byref(sec)) == 0, H.ref_last_error()
+        assert mult_timed(hs[0], hs[1], hs[2], hs[3], cR, cQR, t, outs, threads, ctypes.byref(sec)) == 0, H.ref_last_error()
         for k in range(3):
             H.ref_polys_store(outs[k], p(res[k]))                      # download (b200) / copy out (cpu)
         dt = time.perf_counter() - t0

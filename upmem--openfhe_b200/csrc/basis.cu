@@ -555,19 +555,32 @@ tower_scale_kernel(u64* __restrict__ out, const u64* __restrict__ x, size_t npai
         u64* ob = out + ((b * T) << logN) + n;
         ulonglong2 last = make_ulonglong2(0, 0);
         if (MODE == 1) last = *reinterpret_cast<const ulonglong2*>(xb + ((size_t)T << logN));
-        for (u32 i = 0; i < T; i++) {
-            ulonglong2 r = make_ulonglong2(0, 0);
-            if (MODE == 1 || i < sl) {
-                const u64 q = mods[i].q;
-                const ulonglong4 c = k[i];
-                ulonglong2 xv = *reinterpret_cast<const ulonglong2*>(xb + ((size_t)i << logN));
-                if (MODE == 1) {
-                    xv.x = submod(xv.x, shoup(last.x, 1, c.z, q), q);
-                    xv.y = submod(xv.y, shoup(last.y, 1, c.z, q), q);
+        // towers four at a time: the loads of a group are issued together (4 x 16 B in flight per thread — one tower
+        // at a time leaves too little in flight to cover HBM latency)
+        constexpr u32 U = 4;
+        const u32 nread = MODE == 1 ? T : sl;
+        for (u32 i0 = 0; i0 < T; i0 += U) {
+            ulonglong2 xv[U];
+#pragma unroll
+            for (u32 u = 0; u < U; u++)
+                if (i0 + u < nread) xv[u] = *reinterpret_cast<const ulonglong2*>(xb + ((size_t)(i0 + u) << logN));
+#pragma unroll
+            for (u32 u = 0; u < U; u++) {
+                const u32 i = i0 + u;
+                if (i >= T) break;
+                ulonglong2 r = make_ulonglong2(0, 0);
+                if (i < nread) {
+                    const u64 q = mods[i].q;
+                    const ulonglong4 c = k[i];
+                    ulonglong2 v = xv[u];
+                    if (MODE == 1) {
+                        v.x = submod(v.x, shoup(last.x, 1, c.z, q), q);
+                        v.y = submod(v.y, shoup(last.y, 1, c.z, q), q);
+                    }
+                    r = make_ulonglong2(shoup(v.x, c.x, c.y, q), shoup(v.y, c.x, c.y, q));
                 }
-                r = make_ulonglong2(shoup(xv.x, c.x, c.y, q), shoup(xv.y, c.x, c.y, q));
+                *reinterpret_cast<ulonglong2*>(ob + ((size_t)i << logN)) = r;
             }
-            *reinterpret_cast<ulonglong2*>(ob + ((size_t)i << logN)) = r;
         }
     }
 }
