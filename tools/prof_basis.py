@@ -46,6 +46,16 @@ with pkg.Backend(0, "arena_mb=1024") as be:
     ms = timed(be, lambda: plan.drop_last_element_and_scale(dr, dqp, batch, 0))
     out["drop_last_element_and_scale"] = {"ms": ms, "polys_per_s": batch / (ms * 1e-3),
                                           "towers": sq + sp}
+    # HPSPOVERQ tails (tower_scale_kernel): 8 B in + 8 B out per coefficient per tower
+    T1 = sq + sp - 1
+    rq1 = pkg.RingView(ring, 0, T1)
+    ts = pkg.TowerScale(rq1, [int(v) // 3 for v in q[:T1]])
+    ms = timed(be, lambda: ts.scale_and_round_p_over_q(dr, dqp, batch))
+    out["scale_and_round_p_over_q"] = {"ms": ms, "hbm_gbs": batch * n * (2 * T1 + 1) * 8 / (ms * 1e-3) / 1e9, "towers": T1}
+    ms = timed(be, lambda: ts.expand_crt_basis_ql_hat(dr, dq, sq, batch))
+    out["expand_crt_basis_ql_hat"] = {"ms": ms, "hbm_gbs": batch * n * (sq + T1) * 8 / (ms * 1e-3) / 1e9, "towers": T1}
+    ts.close()
+    rq1.close()
     print(json.dumps(out))
     for o in (q2p, p2q, plan, rq, rp):
         o.close()

@@ -537,11 +537,13 @@ cudaError_t launch_rescale_spread(uint64_t* tmp, const uint64_t* last, size_t ba
 
 // ---- BFV HPSPOVERQ tails ----------------------------------------------------------------------------------------
 // One thread per coefficient pair of one batch item, towers in a loop (every row segment is contiguous in n).
-// k[i] = {c_i, c_i', one_i' = floor(2^64 / q_i), -}.
+// k[i] = {c_i, c_i', M_i = q_i * floor(2^63 / q_i), -}.
 //   mode 0 (ExpandCRTBasisQlHat, dcrtpoly-impl.h:1514-1534): x over [B][sl][N] -> out over [B][T][N]:
 //          out_i = x_i * c_i (i < sl), 0 (sl <= i < T)
 //   mode 1 (ScaleAndRoundPOverQ, dcrtpoly-impl.h:2052-2066): x over [B][T+1][N] -> out over [B][T][N]:
-//          out_i = (x_i - (x_T mod q_i)) * c_i; the last tower's residue can exceed q_i, ModSubEq reduces it first
+//          out_i = (x_i - (x_T mod q_i)) * c_i; the last tower's residue can exceed q_i (ModSubEq reduces it first).
+//          Here the difference is formed as x_i + M_i - x_T with M_i the multiple of q_i next below 2^63: x_T < 2^62 <= M_i,
+//          the sum stays below 2^64, and the Shoup product is exact for any 64-bit operand — one product per coefficient
 template <int MODE>
 __global__ void __launch_bounds__(256)
 tower_scale_kernel(u64* __restrict__ out, const u64* __restrict__ x, size_t npairs, u32 logN, u32 sl, u32 T,
@@ -573,9 +575,9 @@ tower_scale_kernel(u64* __restrict__ out, const u64* __restrict__ x, size_t npai
                     const u64 q = mods[i].q;
                     const ulonglong4 c = k[i];
                     ulonglong2 v = xv[u];
-                    if (MODE == 1) {
-                        v.x = submod(v.x, shoup(last.x, 1, c.z, q), q);
-                        v.y = submod(v.y, shoup(last.y, 1, c.z, q), q);
+                    if (MODE == 1) {                    // x_i + M_i - x_p: congruent to x_i - x_p, non-negative, below 2^64
+                        v.x = v.x + c.z - last.x;
+                        v.y = v.y + c.z - last.y;
                     }
                     r = make_ulonglong2(shoup(v.x, c.x, c.y, q), shoup(v.y, c.x, c.y, q));
                 }
@@ -597,7 +599,7 @@ __global__ void tower_scale_scalar_kernel(u64* __restrict__ out, const u64* __re
                 const u64 q = mods[i].q;
                 const ulonglong4 c = k[i];
                 u64 xv = x[b * xT + i];
-                if (MODE == 1) xv = submod(xv, shoup(x[b * xT + T], 1, c.z, q), q);
+                if (MODE == 1) xv = xv + c.z - x[b * xT + T];
                 r = shoup(xv, c.x, c.y, q);
             }
             out[b * T + i] = r;

@@ -1288,7 +1288,7 @@ extern "C" int fhe_tower_scale_create(fhe_ring* ring, const uint64_t* c, fhe_tow
     for (uint32_t i = 0; i < T; i++) {
         const uint64_t qi = ring->q[i];
         if (c[i] >= qi) return fail(FHE_EINVAL, "fhe_tower_scale_create: constant %u is not reduced modulo its tower", i);
-        k[i] = make_ulonglong4(c[i], host::shoup_companion(c[i], qi), host::shoup_companion(1, qi), 0);
+        k[i] = make_ulonglong4(c[i], host::shoup_companion(c[i], qi), qi * ((1ull << 63) / qi), 0);   // {c, c', M_i}
     }
     auto* p = new fhe_tower_scale;
     p->ctx = ring->ctx; p->ring = ring;
