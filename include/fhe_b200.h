@@ -223,6 +223,10 @@ int fhe_tower_scale_destroy(fhe_tower_scale* plan);
  * zero.  Format preserved. */
 int fhe_expand_crt_basis_ql_hat(fhe_tower_scale* plan, uint32_t size_ql, fhe_dptr dst_q, fhe_dptr src_ql, size_t batch,
                                 int stream);
+/* DCRTPolyImpl::Times(const std::vector<NativeInteger>&) / TimesNoCheck (dcrtpoly-impl.h:617-638): every tower times its
+ * own constant, c_i reduced modulo q_i by the caller (NativeVectorT::ModMulEq reduces an oversized scalar first,
+ * mubintvecnat.cpp:370-385).  dst may be src.  Format preserved. */
+int fhe_dcrt_times_towers(fhe_tower_scale* plan, fhe_dptr dst, fhe_dptr src, size_t batch, int stream);
 /* DCRTPolyImpl::ScaleAndRoundPOverQ (dcrtpoly-impl.h:2052-2066) with c = pInvModq over the ring Q (T towers): src over
  * Q plus one extra tower p [batch][T+1][N] -> dst over Q: ((x_i - (x_p mod q_i)) mod q_i) * c_i.  Format preserved. */
 int fhe_scale_and_round_p_over_q(fhe_tower_scale* plan, fhe_dptr dst_q, fhe_dptr src_qp, size_t batch, int stream);

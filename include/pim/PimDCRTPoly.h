@@ -318,6 +318,13 @@ public:
                       "ExpandCRTBasisQlHat");
     return out;
   }
+  /* dcrtpoly-impl.h:617-627: Times(const std::vector<NativeInteger>&), one constant per tower */
+  PimDCRTPoly Times(const PimTowerScale &plan) const {
+    if (ring_->GetNumTowers() != plan.Ring()->GetNumTowers()) throw pim_math_error("tower size mismatch; cannot multiply");
+    PimDCRTPoly out(ring_, batch_, format_, nullptr, stream_);
+    PimManager::check(fhe_dcrt_times_towers(plan.handle(), out.d_, d_, batch_, stream_), "Times");
+    return out;
+  }
   /* dcrtpoly-impl.h:2052-2066 (in place in the reference): this over plan.Ring() plus one tower */
   PimDCRTPoly ScaleAndRoundPOverQ(const PimTowerScale &plan) const {
     if (ring_->GetNumTowers() != plan.Ring()->GetNumTowers() + 1)

@@ -615,9 +615,14 @@ inline bool resident_fast_expand_pl_over_q(PimManager *pim, const Towers &a, std
 template <class Towers, class IntVec>
 inline bool resident_tower_scale(PimManager *pim, int mode, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
                                  std::shared_ptr<Resident> &rout, const IntVec &c) {
+  /* mode 2: Times(const std::vector<NativeInteger>&) (dcrtpoly-impl.h:617-627) = mode 0 over all towers with the
+   * constants reduced first, as NativeVectorT::ModMulEq does */
+  const bool times = mode == 2;
+  if (times) mode = 0;
   const size_t T = out.size(), sl = mode == 0 ? a.size() : T;
   if (!pim || a.empty() || T == 0 || c.size() < sl) return false;
   if (mode == 0 ? a.size() > T : a.size() != T + 1) return false;
+  if (times && a.size() != T) return false;
   auto da = ensure_device(pim, a, ra);
   auto r = new_resident(pim, out);
   struct Entry {
@@ -630,7 +635,10 @@ inline bool resident_tower_scale(PimManager *pim, int mode, const Towers &a, std
   {
     std::lock_guard<std::mutex> lock(mu);
     std::vector<uint64_t> k(T, 0);
-    for (size_t i = 0; i < sl; i++) k[i] = c[i].ConvertToInt();
+    for (size_t i = 0; i < sl; i++) {
+      k[i] = c[i].ConvertToInt();
+      if (times) k[i] %= out[i].GetModulus().ConvertToInt();
+    }
     auto key = std::make_tuple(r->ring.get(), (const void *)&c[0], sl);
     auto it = cache.find(key);
     if (it == cache.end() || it->second.c != k) {

@@ -357,6 +357,21 @@ def patch_impl(text):
                 "        }\n"
                 "    }\n"
                 "    const usint sizeQ   = m_vectors.size() - 1;\n", rel)
+    # Times(const std::vector<NativeInteger>&) (const): one constant per tower
+    sig = ("DCRTPolyImpl<VecType> DCRTPolyImpl<VecType>::Times(const std::vector<NativeInteger>& rhs) const {\n"
+           "    if (m_vectors.size() != rhs.size())\n"
+           "        OPENFHE_THROW(math_error, \"tower size mismatch; cannot multiply\");\n")
+    text = once(text, sig,
+                "DCRTPolyImpl<VecType> DCRTPolyImpl<VecType>::Times(const std::vector<NativeInteger>& rhs) const {\n"
+                "    if (m_vectors_.size() != rhs.size())\n"
+                "        OPENFHE_THROW(math_error, \"tower size mismatch; cannot multiply\");\n"
+                "    if (pim && !m_vectors_.empty()) {\n"
+                "        DCRTPolyImpl<VecType> dev(m_params, m_format, false);\n"
+                "        if (pimhook::resident_tower_scale(pim.get(), 2, m_vectors_, pimres_, dev.m_vectors_, dev.pimres_, rhs)) {\n"
+                "            dev.pim = pim;\n"
+                "            return dev;\n"
+                "        }\n"
+                "    }\n", rel)
     # ApproxModDown (const, EVALUATION input over QP, returns a polynomial over Q)
     sig = ("    usint sizeQP = m_vectors.size();\n    usint sizeP  = paramsP->GetParams().size();\n    usint sizeQ  = sizeQP - sizeP;\n")
     text = once(text, sig,

@@ -541,6 +541,16 @@ int ref_polys_expand_ql_hat(ref_polys* a, ref_ctx* Q, const uint64_t* c) {
     if (rc) g_ref_err = err;
     return rc;
 }
+// DCRTPoly::Times(const std::vector<NativeInteger>&) (dcrtpoly-impl.h:617-627): new batch, one constant per tower
+ref_polys* ref_polys_times_towers(const ref_polys* a, const uint64_t* c) {
+    auto* r = new ref_polys{a->ctx, {}};
+    std::vector<NativeInteger> k(a->ctx->T);
+    for (uint32_t i = 0; i < a->ctx->T; i++) k[i] = NativeInteger(c[i]);
+    serial_omp([&] {
+        for (auto& poly : a->v) r->v.push_back(poly.Times(k));
+    });
+    return r;
+}
 // DCRTPoly::ScaleAndRoundPOverQ (dcrtpoly-impl.h:2052-2066), in place: Q plus one tower -> Q
 int ref_polys_scale_round_p_over_q(ref_polys* a, ref_ctx* Q, const uint64_t* pinv_modq) {
     int rc = 0;

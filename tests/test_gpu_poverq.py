@@ -125,6 +125,10 @@ def test_tower_scale_edge_cases(pkg, backend, oracle):
     dy = d.put(y)
     plan.expand_crt_basis_ql_hat(out, dy, 2, 5)
     assert np.array_equal(backend.d2h(out, 5 * sq).reshape(5, sq, 1), oracle.expand_ql_hat(y, n, q[:sq].copy(), 2, k[:2]))
+    plan.times(out, dy, 0)
+    d3 = d.put(z[:, :sq].copy())
+    plan.times(d3, d3, 5)                                                # Times(vector<NativeInteger>), in place
+    assert np.array_equal(backend.d2h(d3, 5 * sq).reshape(5, sq, 1), oracle.expand_ql_hat(z[:, :sq].copy(), n, q[:sq].copy(), sq, k))
     plan.scale_and_round_p_over_q(out, dz, 0)                            # empty batch: nothing to do
     with pytest.raises(pkg.FheError):
         plan.expand_crt_basis_ql_hat(out, dy, 4, 5)                      # more source towers than the ring has
@@ -164,3 +168,25 @@ def test_bfv_hps_p_over_q_mult_reference_golden(pkg, backend, oracle, case):
     for k in range(4):
         assert np.array_equal(backend.d2h(din[k], ins[k].size).reshape(ins[k].shape), ins[k]), "input modified"
     mult.close(); d.close(); ring.close()
+
+
+@pytest.mark.parametrize("nbits,n,towers,batch", [(60, 1 << 12, 5, 3), (45, 1 << 14, 9, 2)])
+def test_times_tower_constants_vs_oracle(pkg, backend, oracle, nbits, n, towers, batch):
+    """DCRTPolyImpl::Times(const std::vector<NativeInteger>&) (dcrtpoly-impl.h:617-627), out of place and in place."""
+    q, psi = oracle.gen_params(nbits, n, towers)
+    ring = pkg.Ring(backend, n, q, psi)
+    k = constants(oracle, q, 31)
+    plan = pkg.TowerScale(ring, k)
+    x = oracle.fill_ring(batch, n, q, 32)
+    x[0, :, 0] = q - 1
+    want = oracle.expand_ql_hat(x, n, q, towers, k)
+    for a in range(batch):
+        for i in range(0, towers, 2):
+            assert int(want[a, i, 0]) == int(x[a, i, 0]) * int(k[i]) % int(q[i])
+    d = Dev(backend)
+    dx, out = d.put(x), d.new(x.size)
+    plan.times(out, dx, batch)
+    assert np.array_equal(backend.d2h(out, x.size).reshape(x.shape), want)
+    plan.times(dx, dx, batch)
+    assert np.array_equal(backend.d2h(dx, x.size).reshape(x.shape), want)
+    plan.close(); d.close(); ring.close()

@@ -449,6 +449,22 @@ def test_resident_p_over_q_tails_and_reverse_expand(hooked, oracle, pkg):
         assert cpu_moved == (0, 0), name
         assert np.array_equal(got, cpu), name
         assert np.array_equal(got, want()), name + " vs oracle"
+    # Times(const std::vector<NativeInteger>&): device result born on the device; constants above q_i are reduced first
+    H.ref_polys_times_towers.restype = vp
+    H.ref_polys_times_towers.argtypes = [vp, vp]
+    big = (k[:sq] + q[:sq]).astype(np.uint64)                # unreduced, as NativeVectorT::ModMulEq accepts them
+    for attach in (True, False):
+        h = H.ref_polys_load(cQ, p(x), batch, 0)
+        if attach:
+            assert H.ref_polys_set_pim(h, 1) == 0, H.ref_last_error()
+        c0 = counters(H)
+        hr = H.ref_polys_times_towers(h, p(big))
+        c1 = counters(H)
+        assert (c1[0] - c0[0], c1[1] - c0[1]) == ((batch, 0) if attach else (0, 0))
+        res = np.empty((batch, sq, n), np.uint64)
+        H.ref_polys_store(hr, p(res))
+        assert np.array_equal(res, oracle.expand_ql_hat(x, n, q[:sq].copy(), sq, k[:sq])), attach
+        H.ref_polys_free(hr); H.ref_polys_free(h)
     for c in (cQ, cP, cQP, cPQ, cQ1):
         H.ref_ctx_destroy(c)
 

@@ -53,6 +53,8 @@ def ref():
     R.ref_polys_fast_expand_pl_over_q.argtypes = [vp, vp, vp, vp]
     R.ref_polys_expand_ql_hat.argtypes = [vp, vp, vp]
     R.ref_polys_scale_round_p_over_q.argtypes = [vp, vp, vp]
+    R.ref_polys_times_towers.restype = vp
+    R.ref_polys_times_towers.argtypes = [vp, vp]
     R.ref_bfv_hps_p_over_q_mult.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp)]
     R.ref_bfv_hps_mult.argtypes = [vp, vp, vp, vp, vp, vp, u64, ctypes.POINTER(vp)]
     return R
@@ -368,3 +370,19 @@ def test_bfv_hps_p_over_q_mult_core_matches_reference(oracle, ref, nbits, n, sq,
         ref.ref_polys_free(h)
     for c in (cQ, cR, cQR):
         ref.ref_ctx_destroy(c)
+
+
+def test_times_tower_constants_matches_reference(oracle, ref):
+    """DCRTPolyImpl::Times(const std::vector<NativeInteger>&) (dcrtpoly-impl.h:617-627) vs the restated per-tower product."""
+    n, towers, B = 256, 4, 2
+    q, psi = oracle.gen_params(60, n, towers)
+    c = ref.ref_ctx_create(n, towers, p(q), p(psi))
+    k = oracle.fill_ring(1, 1, q.copy(), 5).reshape(-1).copy()
+    x = oracle.fill_ring(B, n, q, 6)
+    x[0, :, 0] = q - 1
+    hx = ref.ref_polys_load(c, p(x), B, 0)
+    hr = ref.ref_polys_times_towers(hx, p(k))
+    res = np.empty_like(x)
+    ref.ref_polys_store(hr, p(res))
+    assert np.array_equal(res, oracle.expand_ql_hat(x, n, q, towers, k))
+    ref.ref_polys_free(hr); ref.ref_polys_free(hx); ref.ref_ctx_destroy(c)

@@ -69,6 +69,7 @@ SIGNATURES = {
     "fhe_tower_scale_destroy": (ci, [vp]),
     "fhe_expand_crt_basis_ql_hat": (ci, [vp, u32, u64, u64, sz, ci]),
     "fhe_scale_and_round_p_over_q": (ci, [vp, u64, u64, sz, ci]),
+    "fhe_dcrt_times_towers": (ci, [vp, u64, u64, sz, ci]),
     "fhe_scale_round_create": (ci, [vp, u32, ci, vp, vp, ctypes.POINTER(vp)]),
     "fhe_scale_round_destroy": (ci, [vp]),
     "fhe_scale_and_round": (ci, [vp, u64, u64, sz, ci]),

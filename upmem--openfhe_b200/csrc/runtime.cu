@@ -1309,7 +1309,8 @@ static int tower_scale_run(fhe_tower_scale* p, int mode, uint32_t sl, fhe_dptr d
     if (mode == 0 && (sl == 0 || sl > T)) return fail(FHE_EINVAL, "%s: size_ql must be in [1, %u]", who, T);
     if (batch == 0) return FHE_OK;
     if (!dst || !src) return fail(FHE_EINVAL, "%s: null device pointer", who);
-    if (dst == src) return fail(FHE_EINVAL, "%s: dst must not be src (different tower counts)", who);
+    if (dst == src && !(mode == 0 && sl == T))
+        return fail(FHE_EINVAL, "%s: dst must not be src (different tower counts)", who);
     CUDA_TRY(launch_tower_scale(mode, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, batch, p->ring->dev.logN, sl, T,
                                 p->ring->dev.mods, (const ulonglong4*)p->d_k, s));
     return FHE_OK;
@@ -1318,6 +1319,10 @@ static int tower_scale_run(fhe_tower_scale* p, int mode, uint32_t sl, fhe_dptr d
 extern "C" int fhe_expand_crt_basis_ql_hat(fhe_tower_scale* p, uint32_t size_ql, fhe_dptr dst_q, fhe_dptr src_ql, size_t batch,
                                            int stream) {
     return tower_scale_run(p, 0, size_ql, dst_q, src_ql, batch, stream, "fhe_expand_crt_basis_ql_hat");
+}
+extern "C" int fhe_dcrt_times_towers(fhe_tower_scale* p, fhe_dptr dst, fhe_dptr src, size_t batch, int stream) {
+    if (!p) return fail(FHE_EINVAL, "null tower-scale plan");
+    return tower_scale_run(p, 0, p->ring->dev.T, dst, src, batch, stream, "fhe_dcrt_times_towers");
 }
 extern "C" int fhe_scale_and_round_p_over_q(fhe_tower_scale* p, fhe_dptr dst_q, fhe_dptr src_qp, size_t batch, int stream) {
     return tower_scale_run(p, 1, 0, dst_q, src_qp, batch, stream, "fhe_scale_and_round_p_over_q");

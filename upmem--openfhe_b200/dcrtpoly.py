@@ -415,6 +415,10 @@ class TowerScale:
     def scale_and_round_p_over_q(self, dst_q, src_qp, batch, stream=0):
         N.check(N.lib.fhe_scale_and_round_p_over_q(self.h, dst_q, src_qp, batch, stream))
 
+    def times(self, dst, src, batch, stream=0):
+        """DCRTPolyImpl::Times(const std::vector<NativeInteger>&) (dcrtpoly-impl.h:617-627); dst may be src."""
+        N.check(N.lib.fhe_dcrt_times_towers(self.h, dst, src, batch, stream))
+
 
 class ScaleRound:
     """DCRTPolyImpl::ScaleAndRound(paramsOutput, ...) (dcrtpoly-impl.h:1876-1960): `ring` is the input basis, the output
