@@ -457,6 +457,23 @@ def ntt_extra(pkg, be):
                 pkg._native.check(lib.fhe_automorphism(ring.h, dst, src, batch, 5, fmt, 0))
             ms = be.timer_stop(0) / reps
             out[name] = {"ms": ms, "coeff_per_s": words / (ms * 1e-3), "hbm_gbs": 16 * words / (ms * 1e-3) / 1e9}
+        # the two-argument form (PrecomputeAutoMap table resident in HBM, poly-impl.h:368-380)
+        import ctypes as _ct
+        import numpy as _np
+        amap = _np.empty(n, _np.uint32)
+        pkg._native.check(lib.fhe_precompute_automap(n, 5, amap.ctypes.data_as(_ct.c_void_p)))
+        dmap = be.alloc(n * 4)
+        pkg._native.check(lib.fhe_h2d(be.h, dmap, amap.ctypes.data_as(_ct.c_void_p), n * 4, 0))
+        be.sync()
+        for _ in range(2):
+            pkg._native.check(lib.fhe_automorphism_map(ring.h, dst, src, batch, dmap, 0))
+        be.sync()
+        be.timer_start(0)
+        for _ in range(reps):
+            pkg._native.check(lib.fhe_automorphism_map(ring.h, dst, src, batch, dmap, 0))
+        ms = be.timer_stop(0) / reps
+        out["automorphism_map_n65536_t30_b64"] = {"ms": ms, "coeff_per_s": words / (ms * 1e-3), "hbm_gbs": 16 * words / (ms * 1e-3) / 1e9}
+        be.free(dmap)
         be.free(src); be.free(dst)
         ring.close()
         # RNS basis conversion (hybrid key-switching shapes): ApproxSwitchCRTBasis Q -> P, ApproxModUp, ApproxModDown, rescale
