@@ -42,6 +42,11 @@ def run_set(pkg, backend, oracle, n, aq, apsi, sq, sl, batch, seed, check):
     q2pl.fast_expand_crt_basis_pl_over_q(pl2ql, out, dx, batch)
     check("fast_expand_pl_over_q", backend.d2h(out, batch * 2 * sl * n).reshape(batch, 2 * sl, n), x)
     assert np.array_equal(backend.d2h(dx, x.size).reshape(x.shape), x), "source modified"
+    with pytest.raises(pkg.FheError):
+        q2pl.fast_expand_crt_basis_pl_over_q(pl2ql, dx, dx, batch)       # in place is refused
+    if sl != sq:
+        with pytest.raises(pkg.FheError):
+            q2pl.fast_expand_crt_basis_pl_over_q(q2p, out, dx, batch)    # second basis must start at Pl
     # ExpandCRTBasisQlHat: Ql -> Q
     c = constants(oracle, q[:sl], seed + 1)
     y = oracle.fill_ring(batch, n, q[:sl].copy(), seed + 2)

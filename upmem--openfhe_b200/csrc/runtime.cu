@@ -1255,6 +1255,8 @@ extern "C" int fhe_fast_expand_crt_basis_pl_over_q(fhe_basis* q2pl, fhe_basis* p
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
     if (!dst_qlpl || !src_q) return fail(FHE_EINVAL, "%s: null device pointer", who);
+    if (dst_qlpl == src_q) return fail(FHE_EINVAL, "%s: dst must not be src (different tower counts)", who);
+    if (pl2ql->to->dev.T != q2pl->dev.sp) return fail(FHE_EINVAL, "%s: Ql and Pl must have the same number of towers", who);
     if ((rc = basis_exact_ready(pl2ql))) return rc;
     const uint32_t logN = q2pl->from->dev.logN, sq = q2pl->dev.sq, spl = q2pl->dev.sp, sql = pl2ql->dev.sp;
     uint64_t* dst = (uint64_t*)(uintptr_t)dst_qlpl;
