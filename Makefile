@@ -10,8 +10,8 @@ CU      := $(CSRC)/elementwise.cu $(CSRC)/ntt.cu $(CSRC)/modops.cu $(CSRC)/autom
 OBJ     := $(patsubst $(CSRC)/%.cu,$(LIBDIR)/obj/%.o,$(CU))
 HDR     := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h include/pim/*.h)
 
-.PHONY: all lib oracle ref host clean
-all: lib oracle host
+.PHONY: all lib oracle ref host tools clean
+all: lib oracle host tools
 lib: $(LIBDIR)/libfhe_b200.so
 $(LIBDIR)/obj/%.o: $(CSRC)/%.cu $(HDR)
 	@mkdir -p $(dir $@)
@@ -28,5 +28,10 @@ tests/cpp/bin/pim_surface_test: tests/cpp/pim_surface_test.cpp $(HDR)
 	@mkdir -p $(dir $@)
 	g++ -std=c++17 -O2 -Wall -Iinclude -Ioracle $< -o $@ -L$(LIBDIR) -lfhe_b200 -Loracle -lfhe_oracle \
 	    -Wl,-rpath,'$$ORIGIN/../../../$(LIBDIR)' -Wl,-rpath,'$$ORIGIN/../../../oracle'
+# measurement tools that run on the GPU box (built here, travel with the snapshot)
+tools: tools/bin/int_probe
+tools/bin/int_probe: tools/int_probe.cu
+	@mkdir -p $(dir $@)
+	$(NVCC) -gencode arch=compute_100a,code=sm_100a -O3 -o $@ $<
 clean:
-	rm -rf $(LIBDIR) && $(MAKE) -C oracle clean
+	rm -rf $(LIBDIR) tools/bin && $(MAKE) -C oracle clean

@@ -1,21 +1,28 @@
 #!/usr/bin/env python
-"""bench.py — RNS coefficient-ops/s of the B200 backend on BASELINE.json's headline configuration.
+"""bench.py — RNS coefficient-ops/s of the B200 backend on BASELINE.json's metric: add, mult AND the NTT.
 
-Workload (configs[1]): DCRTPoly add + mult, N = 2^14, 8 towers of 60-bit primes, batch 256
-polynomials per GPU.  One step = one modadd launch + one modmul launch over the whole batch
-(2 * 256 * 8 * 16384 = 67.1 M coefficient-ops per GPU).  Operands are 268 MB each (805 MB touched
-per launch), several times the 126 MB L2, so no L2 flush is needed between iterations.
+Workload (configs[2]'s ring, the largest single-GPU configuration): N = 2^16, 30 towers of 60-bit primes, batch 1024
+polynomials per GPU (2.01 G coefficients = 16.1 GB per operand, two operands resident).  One step is the reference
+arm's own operator sequence on every polynomial of the batch, in place as the reference applies it:
+
+    a += b;  a *= b;  a.SwitchFormat();  a.SwitchFormat()        (EVALUATION -> COEFFICIENT -> EVALUATION)
+
+= one modadd launch, one modmul launch, one inverse and one forward NTT (two launches each) over the whole batch:
+4 coefficient-ops per coefficient slot (one op = one output coefficient of modadd, of modmul, or one
+coefficient through one NTT / INTT), 8.05e9 per step per GPU.  The buffers are far larger than the 126 MB L2, so no
+flush is needed between iterations.
 
   value    : device-resident throughput, CUDA events on the launching stream, max over ranks
-  e2e      : same metric through the host-operand C-ABI call (pinned host buffers; H2D of both
-             operands and D2H of both results inside the timed region)
-  roofline : modmul kernel alone, 24 B algorithmic traffic per coefficient, vs the measured HBM peak
-  cpu_baseline : the reference's own CPU path (oracle/_ref) on the host cores, rank 0, N=1 only
+  e2e      : the same step through the host-operand C-ABI call fhe_dcrt_chain_host(ADD, MUL, INTT, NTT): pinned host
+             buffers, H2D of a and b and D2H of a inside the timed region
+  roofline : the dominant kernel family of the step (the forward NTT's two passes) against the integer-pipe roof
+             (Shoup products/s, measured live by fhe_imad_probe), with the element-wise HBM roofline beside it
+  cpu_baseline : the reference's own CPU path (oracle/_ref) on the host cores, rank 0, N=1 only, bounded sample
 
-`--impl reference` times only the CPU reference on the same config/metric.
-Multi-GPU: one process per GPU under torchrun; the global batch (256 x N polynomials) is sharded
-by upmem--openfhe_b200/sharding.py (weak scaling: 256 polynomials per GPU), no data-path collective;
-NCCL carries the barrier, the max-over-ranks reduction and a checksum exchange of the results.
+`--impl reference` times only the CPU reference on the same config/metric (a bounded sample of the batch per step).
+Multi-GPU: one process per GPU under torchrun; the global batch (1024 x N polynomials) is sharded by
+upmem--openfhe_b200/sharding.py (weak scaling: 1024 polynomials per GPU), no data-path collective; NCCL carries the
+barrier, the max-over-ranks reduction and the optional gather of a result block.
 """
 import argparse
 import importlib
@@ -29,10 +36,17 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-N_RING, TOWERS, BATCH, NBITS = 1 << 14, 8, 256, 60
-WORKLOAD = "dcrtpoly add+mult N=2^14 T=8 batch=256 per GPU, 60-bit moduli (BASELINE configs[1])"
+N_RING, TOWERS, BATCH, NBITS = 1 << 16, 30, 1024, 60
+OPS_PER_SLOT = 4                       # modadd, modmul, INTT, NTT
+WORKLOAD = ("dcrtpoly a+=b; a*=b; SwitchFormat x2 (INTT, NTT), in place, N=2^16 T=30 batch=1024 per GPU, "
+            "60-bit moduli (BASELINE configs[2] ring; the metric's add, mult and NTT in one step)")
 METRIC = "rns_coeff_ops_per_sec"
 UNIT = "coeff-ops/s"
+CPU_SAMPLE_BATCH = 64                  # polynomials per CPU step (of the 1024): ~0.3 s per step on 16 cores
+# identical in both arms (the driver compares the dicts key for key)
+CONFIG = {"workload": WORKLOAD, "N": N_RING, "towers": TOWERS, "batch_per_gpu": BATCH, "moduli_bits": NBITS,
+          "ops_per_step": ["modadd", "modmul", "intt", "ntt"], "coeff_ops_per_step_per_gpu": OPS_PER_SLOT * BATCH * TOWERS * N_RING,
+          "l2": "operands 16.1 GB each >> 126 MB L2: no flush needed"}
 
 
 def parse():
@@ -126,23 +140,40 @@ def max_over_ranks(dist, local, x):
     return float(t.item())
 
 
+def cpu_sample_note(batch, steps, what):
+    return (f"{batch} of the {BATCH} polynomials per step (same ring, same four operators: += , *= , SwitchFormat x2 of the "
+            f"reference's DCRTPoly, in place), {what}, {steps} steps")
+
+
+def claim_host_threads():
+    """Before libgomp is loaded: torchrun exports OMP_NUM_THREADS=1, and the reference sizes its thread pool from
+    omp_get_max_threads() in a static constructor (utils/parallel.h:52).  Returns (host threads, the old value)."""
+    was = os.environ.get("OMP_NUM_THREADS")
+    try:
+        n = max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        n = max(1, os.cpu_count() or 1)
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    return n, was
+
+
 def run_reference(args):
-    world, rank, local, _ = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), 0, None
+    rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    threads, omp_was = claim_host_threads()
     from oracle import cpu_baseline
-    r = cpu_baseline.time_addmul(N_RING, TOWERS, BATCH, NBITS, steps=args.steps, warmup=args.warmup)
+    r = cpu_baseline.time_step(N_RING, TOWERS, CPU_SAMPLE_BATCH, NBITS, steps=args.steps, warmup=args.warmup, threads=threads)
     total = sum(r["step_seconds"])
     value = r["coeff_ops_per_step"] * len(r["step_seconds"]) / total
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / len(r["step_seconds"]), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic", "impl": "reference",
-        "config": {"workload": WORKLOAD, "N": N_RING, "towers": TOWERS, "batch_per_gpu": BATCH,
-                   "note": "CPU reference runs ONE GPU's share (batch 256) on the host cores"},
+        "config": CONFIG,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
-                         "sample": f"full batch {BATCH}, in-place += and *= of the reference's DCRTPoly, "
-                                   f"omp-for over the batch, {args.steps} steps"},
+                         "host_threads": r["host_threads"], "omp_num_threads_env_was": omp_was,
+                         "sample": cpu_sample_note(CPU_SAMPLE_BATCH, args.steps, "omp-for over the batch on every host thread")},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -170,11 +201,34 @@ def emit(line):
         os.write(_JSON_FD, data)
 
 
+def host_mem_available():
+    """Bytes of host memory this process can still take (MemAvailable, capped by the cgroup limit if there is one)."""
+    avail = None
+    try:
+        with open("/proc/meminfo") as f:
+            for ln in f:
+                if ln.startswith("MemAvailable:"):
+                    avail = int(ln.split()[1]) * 1024
+    except OSError:
+        pass
+    for lim, cur in (("/sys/fs/cgroup/memory.max", "/sys/fs/cgroup/memory.current"),
+                     ("/sys/fs/cgroup/memory/memory.limit_in_bytes", "/sys/fs/cgroup/memory/memory.usage_in_bytes")):
+        try:
+            v = open(lim).read().strip()
+            if v != "max":
+                room = int(v) - int(open(cur).read().strip())
+                avail = room if avail is None else min(avail, room)
+        except (OSError, ValueError):
+            pass
+    return avail
+
+
 def main():
     args = parse()
     claim_stdout()
     if args.impl == "reference":
         return run_reference(args)
+    host_threads, omp_was = claim_host_threads()
     world, rank, local, dist = dist_setup(args.gpus)
     pkg = importlib.import_module("upmem--openfhe_b200")
     be = pkg.Backend(local, "streams=4,arena_mb=1024")
@@ -184,10 +238,11 @@ def main():
     shard = sharding.plan(BATCH * world, TOWERS, world)[rank]      # this rank's block of the global batch
     assert shard.batch == BATCH and shard.towers == TOWERS
     words = ring.words(BATCH)
-    coeffs = words                                   # coefficient-ops per launch
+    coeffs = words                                   # coefficient slots per GPU
     lib, ADD, MUL = pkg._native.lib, pkg.OP_ADD, pkg.OP_MUL
+    warmup = max(args.warmup, 3)
 
-    da, db, dc, dd = (be.alloc(words * 8) for _ in range(4))
+    da, db = be.alloc(words * 8), be.alloc(words * 8)
     ring.fill_uniform(da, BATCH, 20260002 + shard.b0 * 7919)
     ring.fill_uniform(db, BATCH, 20261002 + shard.b0 * 7919)
     be.sync()
@@ -196,10 +251,12 @@ def main():
     sampler.start()
 
     def step():
-        ring.op(ADD, dc, da, db, BATCH, 0)
-        ring.op(MUL, dd, da, db, BATCH, 0)
+        ring.op(ADD, da, da, db, BATCH, 0)          # a += b
+        ring.op(MUL, da, da, db, BATCH, 0)          # a *= b
+        ring.ntt(da, BATCH, True, 0)                # a.SwitchFormat(): EVALUATION -> COEFFICIENT
+        ring.ntt(da, BATCH, False, 0)               # a.SwitchFormat(): COEFFICIENT -> EVALUATION
 
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warmup):
         step()
     be.sync()
     barrier(dist, local)
@@ -211,101 +268,122 @@ def main():
     launches = lib.fhe_launch_count() - l0
     barrier(dist, local)
     ms = max_over_ranks(dist, local, ms)
-    value = world * 2 * coeffs * args.steps / (ms * 1e-3)
+    value = world * OPS_PER_SLOT * coeffs * args.steps / (ms * 1e-3)
 
-    # ---- roofline of the dominant kernel (modmul), timed alone on its launching stream ----
-    reps = max(20, min(args.steps, 200))
-    for _ in range(3):
-        ring.op(MUL, dd, da, db, BATCH, 0)
-    be.sync()
-    be.timer_start(0)
-    for _ in range(reps):
-        ring.op(MUL, dd, da, db, BATCH, 0)
-    mul_ms = be.timer_stop(0) / reps
-    be.timer_start(0)
-    for _ in range(reps):
-        ring.op(ADD, dc, da, db, BATCH, 0)
-    add_ms = be.timer_stop(0) / reps
+    # ---- rooflines: every kernel family of the step timed alone on its launching stream ----
+    def timed(f, reps):
+        for _ in range(2):
+            f()
+        be.sync()
+        be.timer_start(0)
+        for _ in range(reps):
+            f()
+        return be.timer_stop(0) / reps
+
+    reps = 5
+    fwd_ms = timed(lambda: ring.ntt(da, BATCH, False, 0), reps)
+    inv_ms = timed(lambda: ring.ntt(da, BATCH, True, 0), reps)
+    mul_ms = timed(lambda: ring.op(MUL, da, da, db, BATCH, 0), reps)
+    add_ms = timed(lambda: ring.op(ADD, da, da, db, BATCH, 0), reps)
+    blocks, threads, iters = 148 * 8, 256, 4096
+    p_ms = min(be.imad_probe(blocks, threads, iters) for _ in range(3))
+    shoup_peak = blocks * threads * iters * 8 / (p_ms * 1e-3)
     peaks, peak_src = measured_peaks()
-    alg_bytes = 24 * coeffs
-    achieved = alg_bytes / (mul_ms * 1e-3) / 1e9
-    traffic = None
+    traffic = {}
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         with open(tpath) as f:
-            traffic = json.load(f).get("ew_mul_dram_bytes_per_launch")
-    roofline = {"bound": "hbm", "kernel": "ew_ring_kernel<MUL> (fhe_dcrt_op)", "achieved": achieved,
-                "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                "traffic": traffic, "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": mul_ms,
-                "peak_source": f"{peak_src} copy bandwidth (burst: kernel timed alone)",
-                "frac_of_nominal_8TBs": achieved / 8000.0,
-                "modadd": {"launch_ms": add_ms, "achieved": alg_bytes / (add_ms * 1e-3) / 1e9,
-                           "frac": alg_bytes / (add_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}}
+            traffic = json.load(f)
+    logn = N_RING.bit_length() - 1
+    bf = coeffs * logn / 2                            # (N/2) log2 N butterflies per tower
+    moved = int(traffic.get("ntt_moved_bytes_per_coeff", 32))
+    ew_bytes = 24 * coeffs
+    ew_ach = ew_bytes / (mul_ms * 1e-3) / 1e9
+    roofline = {
+        "bound": "integer pipe", "kernel": "forward NTT (fhe_ntt_forward: all its launches)",
+        "achieved": bf / (fwd_ms * 1e-3), "peak": shoup_peak, "unit": "butterflies/s vs Shoup products/s (mulhi64 + 2 mullo64)",
+        "frac": bf / (fwd_ms * 1e-3) / shoup_peak,
+        "traffic": traffic.get("ntt_fwd_dram_bytes_per_transform_b1024"),
+        "algorithmic_bytes_per_launch": 16 * coeffs, "launch_ms": fwd_ms,
+        "peak_source": "fhe_imad_probe, measured live in this run (148x8 CTAs x 256 threads x 8 chains)",
+        "coeff_per_s": coeffs / (fwd_ms * 1e-3),
+        "inverse": {"launch_ms": inv_ms, "achieved": bf / (inv_ms * 1e-3), "frac": bf / (inv_ms * 1e-3) / shoup_peak,
+                    "coeff_per_s": coeffs / (inv_ms * 1e-3)},
+        "hbm": {"algorithmic_bytes_per_coeff": 16, "moved_bytes_per_coeff": moved,
+                "achieved_gbs_moved": moved * coeffs / (fwd_ms * 1e-3) / 1e9,
+                "frac_of_measured_peak": moved * coeffs / (fwd_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]},
+        "elementwise": {"bound": "hbm", "kernel": "ew_ring_kernel<MUL> (fhe_dcrt_op)", "achieved": ew_ach,
+                        "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ew_ach / peaks["hbm_gbs"],
+                        "traffic": traffic.get("ew_mul_dram_bytes_per_launch_b1024"),
+                        "algorithmic_bytes_per_launch": ew_bytes, "launch_ms": mul_ms,
+                        "peak_source": f"{peak_src} copy bandwidth (burst: kernel timed alone); above 1.0 = faster than the "
+                                       "driver's plain copy, part of the result is still in L2 when the kernel ends",
+                        "frac_of_nominal_8TBs": ew_ach / 8000.0,
+                        "modadd": {"launch_ms": add_ms, "achieved": ew_bytes / (add_ms * 1e-3) / 1e9,
+                                   "frac": ew_bytes / (add_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}},
+    }
 
-    # ---- end to end: host operands through the C ABI ----
-    ha, pa = be.host_alloc(words)
-    hb, pb = be.host_alloc(words)
-    hc, pc = be.host_alloc(words)
-    hd, pd = be.host_alloc(words)
-    be.d2h(da, words, out=ha)
-    be.d2h(db, words, out=hb)
-    e2e_steps = max(3, min(args.steps, 10))
-    # (i) the reference arm's own step, on host operands: a += b; a *= b in place (one result comes back)
-    for _ in range(2):
-        ring.chain_host([ADD, MUL], ha, hb, BATCH)
+    # ---- end to end: the same step on HOST operands through the C ABI ----
+    # pinned a and b; batch = the largest power-of-two share of the 1024 whose two pinned operands fit in 40 % of the
+    # host memory this rank may take (all 1024 on a box with >= 80 GB free per rank)
+    OPS = [ADD, MUL, pkg.OP_INTT, pkg.OP_NTT]
+    item_bytes = TOWERS * N_RING * 8
+    avail = host_mem_available()
+    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", world))
+    e2e_batch = BATCH
+    while e2e_batch > 32 and avail is not None and 2 * e2e_batch * item_bytes * local_world > 0.4 * avail:
+        e2e_batch //= 2
+    ha = hb = None
+    while ha is None:
+        try:
+            ha, pa = be.host_alloc(e2e_batch * TOWERS * N_RING)
+            hb, pb = be.host_alloc(e2e_batch * TOWERS * N_RING)
+        except pkg.FheError:
+            if ha is not None:
+                be.host_free(pa)
+                ha = None
+            if e2e_batch <= 32:
+                raise
+            e2e_batch //= 2
+    e2e_words = e2e_batch * TOWERS * N_RING
+    ring.fill_uniform(da, BATCH, 20260002 + shard.b0 * 7919)
+    be.d2h(da, e2e_words, out=ha)
+    be.d2h(db, e2e_words, out=hb)
+    e2e_steps = max(2, min(args.steps, 3))
+    ring.chain_host(OPS, ha, hb, e2e_batch)                     # warm-up (also first touch of the pipeline's buffers)
     barrier(dist, local)
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        ring.chain_host([ADD, MUL], ha, hb, BATCH)
+        ring.chain_host(OPS, ha, hb, e2e_batch)
     be.sync()
     e2e_s = max_over_ranks(dist, local, time.perf_counter() - t0)
-    # (ii) the out-of-place form (a + b and a * b both returned): twice the D2H bytes
-    be.d2h(da, words, out=ha)
-    ring.multi_op_host([ADD, MUL], [hc, hd], ha, hb, BATCH)
-    barrier(dist, local)
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        ring.multi_op_host([ADD, MUL], [hc, hd], ha, hb, BATCH)
-    be.sync()
-    e2e2_s = max_over_ranks(dist, local, time.perf_counter() - t0)
-    # PCIe ceiling for this access pattern: both directions busy at once, pinned memory, same sizes
-    N_ = pkg._native
-    be.sync()
-    t0 = time.perf_counter()
-    N_.check(N_.lib.fhe_h2d(be.h, da, pa, words * 8, 0))
-    N_.check(N_.lib.fhe_d2h(be.h, pc, dc, words * 8, 1))
-    be.sync()
-    pcie_both = words * 8 / (time.perf_counter() - t0) / 1e9
-    ring.fill_uniform(da, BATCH, 20260002 + shard.b0 * 7919)
-    be.sync()
-    e2e = {"value": world * 2 * coeffs * e2e_steps / e2e_s, "unit": UNIT,
-           "pcie": {"h2d_gbs": 2 * words * 8 / (e2e_s / e2e_steps) / 1e9,
-                    "d2h_gbs": words * 8 / (e2e_s / e2e_steps) / 1e9,
-                    "ceiling_gbs_each_way_bidirectional": pcie_both,
-                    "note": "the host-operand path is PCIe-bound: 16 B up and 8 B down per coefficient slot "
-                            "for 2 coefficient-ops"},
-           "h2d_bytes_per_step": 2 * words * 8, "d2h_bytes_per_step": words * 8, "steps": e2e_steps,
-           "ms_per_step": 1e3 * e2e_s / e2e_steps,
-           "api": "fhe_dcrt_chain_host(ADD, MUL): a += b; a *= b on pinned host operands (the reference arm's "
-                  "step), chunked H2D/kernels/D2H over 4 streams",
-           "out_of_place": {"value": world * 2 * coeffs * e2e_steps / e2e2_s, "ms_per_step": 1e3 * e2e2_s / e2e_steps,
-                            "h2d_bytes_per_step": 2 * words * 8, "d2h_bytes_per_step": 2 * words * 8,
-                            "api": "fhe_dcrt_multi_op_host(ADD, MUL): a + b and a * b both returned"}}
+    e2e = {"value": world * OPS_PER_SLOT * e2e_words * e2e_steps / e2e_s, "unit": UNIT,
+           "h2d_bytes_per_step": 2 * e2e_words * 8, "d2h_bytes_per_step": e2e_words * 8, "steps": e2e_steps,
+           "ms_per_step": 1e3 * e2e_s / e2e_steps, "batch_per_gpu": e2e_batch,
+           "pcie": {"h2d_gbs": 2 * e2e_words * 8 / (e2e_s / e2e_steps) / 1e9,
+                    "d2h_gbs": e2e_words * 8 / (e2e_s / e2e_steps) / 1e9,
+                    "note": "PCIe-bound: 16 B up and 8 B down per coefficient slot for 4 coefficient-ops"},
+           "api": "fhe_dcrt_chain_host(ADD, MUL, INTT, NTT): a += b; a *= b; a.SwitchFormat() x2 on pinned host operands "
+                  "(the reference arm's step), chunked H2D / kernels / D2H over 4 streams",
+           "host_mem_available_gb": None if avail is None else avail / 1e9}
+    be.host_free(pa)
+    be.host_free(pb)
 
-    # ---- optional result gather (north_star: "NCCL over NVLink only to gather results"): every rank receives every
-    # rank's product of one step, HBM to HBM; device-timed on torch's stream, max over ranks ----
+    # ---- optional result gather (north_star: "NCCL over NVLink only to gather results"): every rank receives a
+    # 64-polynomial block (1 GB) of every rank's result, HBM to HBM; device-timed on torch's stream, max over ranks ----
     gather = None
     if dist is not None:
         import torch
-        step()
+        g_batch = 64
+        g_words = g_batch * TOWERS * N_RING
         be.sync()
         dev = torch.device("cuda", local)
-        g = sharding.gather_device(dd, words, dist, dev)             # warm-up: NCCL channels, output allocation
+        g = sharding.gather_device(da, g_words, dist, dev)           # warm-up: NCCL channels, output allocation
         torch.cuda.synchronize()
         own = g[rank, :4096].cpu().numpy().view("uint64")
-        assert (own == be.d2h(dd, 4096)).all(), "gathered block differs from this rank's result"
+        assert (own == be.d2h(da, 4096)).all(), "gathered block differs from this rank's result"
         for _ in range(2):                                            # NCCL sets its channels up lazily
-            g = sharding.gather_device(dd, words, dist, dev, out=g)
+            g = sharding.gather_device(da, g_words, dist, dev, out=g)
         torch.cuda.synchronize()
         reps_g, rounds = 5, []
         for _ in range(3):                                            # best of three rounds, each max over ranks
@@ -313,22 +391,23 @@ def main():
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             ev0.record()
             for _ in range(reps_g):
-                g = sharding.gather_device(dd, words, dist, dev, out=g)       # the output buffer is reused
+                g = sharding.gather_device(da, g_words, dist, dev, out=g)       # the output buffer is reused
             ev1.record()
             torch.cuda.synchronize()
             rounds.append(max_over_ranks(dist, local, ev0.elapsed_time(ev1) / reps_g))
         del g
         g_ms = min(rounds)
-        step_ms = ms / args.steps
-        gather = {"what": "all_gather_into_tensor of each rank's modmul result of one step (NCCL over NVLink/NVSwitch)",
-                  "bytes_per_rank": words * 8, "ms": g_ms, "rounds_ms": rounds, "recv_gbs_per_rank": (world - 1) * words * 8 / (g_ms * 1e-3) / 1e9,
-                  "value_with_gather": world * 2 * coeffs / ((step_ms + g_ms) * 1e-3),
-                  "note": "value (without the gather) is the headline; a step moves 1.6 GB through HBM in "
-                          f"{step_ms:.3f} ms, its 268 MB product takes {g_ms:.2f} ms to reach the other {world - 1} GPU(s)"}
+        gather = {"what": f"all_gather_into_tensor of a {g_batch}-polynomial block of each rank's result (NCCL over NVLink/NVSwitch)",
+                  "bytes_per_rank": g_words * 8, "ms": g_ms, "rounds_ms": rounds,
+                  "recv_gbs_per_rank": (world - 1) * g_words * 8 / (g_ms * 1e-3) / 1e9,
+                  "note": "results stay sharded (a full gather is 16.1 GB per rank); value excludes the gather"}
+    roofline["gather"] = gather
 
     sampler.stop_flag = True
     sampler.join()
 
+    be.free(da)
+    be.free(db)
     extra = {}
     if not args.no_extra and rank == 0:
         extra = ntt_extra(pkg, be)
@@ -337,28 +416,28 @@ def main():
     if world == 1 and rank == 0:
         try:
             from oracle import cpu_baseline
-            r = cpu_baseline.time_addmul(N_RING, TOWERS, BATCH, NBITS, steps=5, warmup=1)
+            r = cpu_baseline.time_step(N_RING, TOWERS, CPU_SAMPLE_BATCH, NBITS, steps=5, warmup=1, threads=host_threads)
             med = statistics.median(r["step_seconds"])
             cpu = {"value": r["coeff_ops_per_step"] / med, "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
-                   "sample": f"full batch {BATCH} (same workload), in-place += and *=, omp-for over the batch, median of 5"}
-            if not args.no_extra:     # the reference's own SwitchFormat on the host cores, beside the NTT figure
-                rn = cpu_baseline.time_ntt(1 << 16, 30, 16, NBITS, steps=3, warmup=1)
-                mn = statistics.median(rn["step_seconds"])
-                if "ntt_n65536_t30_b64" in extra:
-                    extra["ntt_n65536_t30_b64"]["cpu_reference"] = {
-                        "coeff_per_s": rn["coeff_ops_per_step"] / mn, "cores": rn["cores"], "kind": rn["kind"],
-                        "sample": "batch 16 of the same ring, forward + inverse SwitchFormat, omp-for over the batch, median of 3"}
+                   "host_threads": r["host_threads"], "omp_num_threads_env_was": omp_was,
+                   "sample": cpu_sample_note(CPU_SAMPLE_BATCH, 5, "omp-for over the batch on every host thread, median")}
+            if r["kind"] == "reference":      # beside it: the reference's OWN parallelism (OpenMP over the towers of one poly)
+                rf = cpu_baseline.time_step(N_RING, TOWERS, 8, NBITS, steps=3, warmup=1, threads=host_threads, faithful=True)
+                mf = statistics.median(rf["step_seconds"])
+                cpu["reference_faithful"] = {
+                    "value": rf["coeff_ops_per_step"] / mf, "unit": UNIT, "cores": rf["cores"],
+                    "sample": cpu_sample_note(8, 3, "serial over the batch, OpenFHE's own omp-for over <= T towers per call "
+                                                    "(dcrtpoly-impl.h:412, utils/parallel.h:112-118), median")}
         except Exception as ex:      # the checker is optional for the product, never the other way round
             cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": str(ex)[:200]}
 
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "warmup": warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "N": N_RING, "towers": TOWERS, "batch_per_gpu": BATCH,
-                       "l2": "operands 268 MB each > 126 MB L2: no flush needed", "parallelism": f"batch-sharded x{world}"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "gather": gather,
+            "config": CONFIG, "parallelism": f"batch-sharded x{world}, no data-path collective",
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": sampler.summary(), "extra": extra,
         }
         emit(line)
@@ -369,19 +448,44 @@ def main():
 
 
 def ntt_extra(pkg, be):
-    """Secondary figures (rank 0): batched forward / inverse NTT at BASELINE configs[2]'s shape
-    (N=2^16, 30 towers; batch cut to 64 so the run stays short, 1 GB in place > L2) against the
-    integer roofline.  Integer roofline = rate of lazy Shoup products (mulhi64 + 2 mullo64, the multiply
-    work of one butterfly) measured live by fhe_imad_probe; achieved = butterflies/s of the transform."""
+    """Secondary figures (rank 0): BASELINE configs[1] (add + mult, N=2^14, 4 and 8 towers, batch 256), the NTT at the
+    other ring sizes against the integer roofline (rate of lazy Shoup products measured live by fhe_imad_probe;
+    achieved = butterflies/s of the transform), the ciphertext pipelines of configs[3] / configs[4] and the
+    neighbouring DCRTPoly methods."""
     out = {}
     try:
+        peaks, _ = measured_peaks()
+        for towers in (4, 8):                          # BASELINE configs[1]: "4 and 8 towers, batch 256"
+            n, batch = 1 << 14, 256
+            q, psi = pkg.gen_params(60, n, towers)
+            ring = pkg.Ring(be, n, q, psi)
+            words = ring.words(batch)
+            a, b, c = (be.alloc(words * 8) for _ in range(3))
+            ring.fill_uniform(a, batch, 20260002); ring.fill_uniform(b, batch, 20261002)
+            res = {}
+            for name, op in (("add", pkg.OP_ADD), ("mul", pkg.OP_MUL)):
+                for _ in range(3):
+                    ring.op(op, c, a, b, batch, 0)
+                be.sync()
+                reps = 50
+                be.timer_start(0)
+                for _ in range(reps):
+                    ring.op(op, c, a, b, batch, 0)
+                ms = be.timer_stop(0) / reps
+                res[name] = {"launch_ms": ms, "coeff_ops_per_s": words / (ms * 1e-3), "hbm_gbs": 24 * words / (ms * 1e-3) / 1e9,
+                             "frac_of_measured_hbm_peak": 24 * words / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
+            res["add_plus_mul_coeff_ops_per_s"] = 2 * words / ((res["add"]["launch_ms"] + res["mul"]["launch_ms"]) * 1e-3)
+            res["note"] = ("operands %d MB each" % (words * 8 >> 20)) + (": the three buffers fit the 126 MB L2 only partly" if towers == 4 else "")
+            out[f"cfg1_addmul_n16384_t{towers}_b256"] = res
+            for p_ in (a, b, c):
+                be.free(p_)
+            ring.close()
         blocks, threads, iters = 148 * 8, 256, 4096
         p_ms = min(be.imad_probe(blocks, threads, iters) for _ in range(3))
         shoup_peak = blocks * threads * iters * 8 / (p_ms * 1e-3)
         out["int_probe"] = {"shoup_products_per_s": shoup_peak, "ms": p_ms,
                             "note": "8 independent chains of mulhi64 + 2 mullo64 per thread, 148x8 CTAs x 256 threads"}
-        peaks, _ = measured_peaks()
-        for logn, towers, batch in ((16, 30, 64), (14, 8, 256)):
+        for logn, towers, batch in ((15, 16, 128), (14, 8, 256)):
             n = 1 << logn
             q, psi = pkg.gen_params(60, n, towers)
             ring = pkg.Ring(be, n, q, psi)

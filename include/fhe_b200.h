@@ -77,7 +77,10 @@ enum {
     FHE_EUNSUPPORTED = -5 /* valid request this build does not implement */
 };
 
-enum { FHE_OP_ADD = 0, FHE_OP_SUB = 1, FHE_OP_MUL = 2 };
+enum { FHE_OP_ADD = 0, FHE_OP_SUB = 1, FHE_OP_MUL = 2,
+       /* accepted by fhe_dcrt_chain_host only: DCRTPolyImpl::SwitchFormat on the running value,
+        * COEFFICIENT -> EVALUATION (forward) and EVALUATION -> COEFFICIENT (inverse) */
+       FHE_OP_NTT = 3, FHE_OP_INTT = 4 };
 enum { FHE_STREAM_LEGACY = -1 };
 
 /* Kernel ids of the legacy descriptor path: the five binaries named in pim/kernel.h:4-8. */
@@ -99,6 +102,10 @@ long fhe_launch_count(void);
 
 /* ---- memory ------------------------------------------------------------------------------- */
 int fhe_alloc(fhe_ctx* ctx, size_t bytes, fhe_dptr* out);        /* 256-byte aligned */
+/* Stream-ordered: a block may be freed as soon as the calls that use it have RETURNED (their launches may still be
+ * pending).  It is handed out again only after everything enqueued, before the fhe_free call, on the streams of this
+ * context (the pool and FHE_STREAM_LEGACY) has completed; an allocation that finds the arena full waits for such
+ * blocks instead of growing.  Work a caller enqueued on streams of its own must be synchronised by the caller. */
 int fhe_free(fhe_ctx* ctx, fhe_dptr p);
 int fhe_arena_stats(fhe_ctx* ctx, size_t* reserved_bytes, size_t* in_use_bytes);
 int fhe_host_alloc(fhe_ctx* ctx, size_t bytes, void** out);      /* pinned host memory */
@@ -319,8 +326,10 @@ int fhe_dcrt_op_host(fhe_ring* ring, int op, uint64_t* dst, const uint64_t* a, c
 int fhe_dcrt_multi_op_host(fhe_ring* ring, const int* ops, int nops, uint64_t* const* dsts,
                            const uint64_t* a, const uint64_t* b, size_t batch);
 /* The reference's in-place operator sequence on host operands (DCRTPolyImpl::operator+= / -= / *=,
- * dcrtpoly-impl.h:398-416, dcrtpoly.h:142-148): for i < nops <= 8, a (ops[i])= b, whole batch, the
- * intermediate values never leave the device; one upload of a and b, one download of a. Blocking. */
+ * dcrtpoly-impl.h:398-416, dcrtpoly.h:142-148, and DCRTPolyImpl::SwitchFormat, dcrtpoly-impl.h:2518-2524): for
+ * i < nops <= 8, a (ops[i])= b, or a.SwitchFormat() for FHE_OP_NTT / FHE_OP_INTT, whole batch; the intermediate
+ * values never leave the device; one upload of a and b (b is not read, and may be NULL, when no op uses it), one
+ * download of a.  Chunks of the batch are pipelined over the stream pool (H2D, kernels, D2H overlap). Blocking. */
 int fhe_dcrt_chain_host(fhe_ring* ring, const int* ops, int nops, uint64_t* a, const uint64_t* b, size_t batch);
 /* in-place transform of a host buffer (inverse = 0 forward, 1 inverse). Blocking. */
 int fhe_ntt_host(fhe_ring* ring, uint64_t* x, size_t batch, int inverse);

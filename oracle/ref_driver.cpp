@@ -853,5 +853,9 @@ ref_polys* ref_polys_deserialize(ref_ctx* c, const uint8_t* bytes, size_t len) {
 }
 
 int ref_max_threads(void) { return omp_get_max_threads(); }
+// Thread count for the reference's own `omp parallel for` regions (the batch loops above pass theirs explicitly).
+// OpenFHE caps its tower loops at the value omp_get_max_threads() had when the library was loaded
+// (ParallelControls::machineThreads, utils/parallel.h:52), so OMP_NUM_THREADS must also be right at load time.
+void ref_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 }  // extern "C"

@@ -4,6 +4,8 @@ Shapes follow the reference's own tests (tiny rings with fixed vectors, SURVEY Â
 BASELINE.json's configs (N = 2^14..2^16 with 60-bit moduli) at batch sizes the oracle finishes in
 seconds; full-size configs are covered by size-independent properties in test_gpu_properties.py.
 """
+import ctypes
+
 import numpy as np
 import pytest
 
@@ -367,3 +369,87 @@ def test_ct_multiply_in_place_and_squaring(pkg, backend, oracle):
     with pytest.raises(pkg.FheError):
         ring.ct_multiply([d0.dptr, d0.dptr, d2.dptr], [d0.dptr, d1.dptr], [d0.dptr, d1.dptr], batch, 0)
     ring.close()
+
+
+# ---- round 2: the bench step through the host-operand call, stream-ordered frees, aliasing forms ----------------
+def test_chain_host_with_switch_format_vs_oracle(pkg, backend, oracle):
+    """a += b; a *= b; a.SwitchFormat() (-> COEFFICIENT); a.SwitchFormat() (-> EVALUATION): bench.py's e2e call."""
+    n, towers, batch = 1 << 14, 4, 80           # several 32 MB chunks over the stream pool
+    q, psi = params(oracle, 60, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q, psi)
+    rng = np.random.default_rng(11)
+    a, b = rand_polys(rng, batch, n, q), rand_polys(rng, batch, n, q)
+    prod = octx.elementwise(MUL, octx.elementwise(ADD, a, b), b)
+    x = a.copy()
+    ring.chain_host([ADD, MUL, pkg.OP_INTT], x, b, batch)
+    assert np.array_equal(x, octx.ntt(prod, inverse=True))
+    x = a.copy()
+    ring.chain_host([ADD, MUL, pkg.OP_INTT, pkg.OP_NTT], x, b, batch)
+    assert np.array_equal(x, prod)
+    # transform-only chain: b is not read and may be absent
+    x = a.copy()
+    n_ops = (ctypes.c_int * 1)(pkg.OP_NTT)
+    pkg._native.check(pkg._native.lib.fhe_dcrt_chain_host(ring.h, n_ops, 1, x.ctypes.data_as(ctypes.c_void_p), None, batch))
+    assert np.array_equal(x, octx.ntt(a, inverse=False))
+    with pytest.raises(pkg.FheError):
+        ring.chain_host([5], x, b, batch)
+    ring.close()
+
+
+def test_free_is_stream_ordered(pkg, backend, oracle):
+    """A block freed while launches that write it are still pending on another stream must not be handed out again
+    before they finish (the arena used to put it straight back on the free list)."""
+    n, towers, batch = 1 << 14, 8, 128          # 128 MB
+    q, psi = params(oracle, 60, n, towers)
+    ring = pkg.Ring(backend, n, q, psi)
+    nbytes = ring.words(batch) * 8
+    pattern = np.arange(4096, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15)
+    for _ in range(3):
+        tmp = backend.alloc(nbytes)
+        for k in range(40):                      # a few ms of pending writes to tmp on stream 2
+            ring.fill_uniform(tmp, batch, 1000 + k, stream=2)
+        backend.free(tmp)                        # enqueue-and-free, as the live intercept does with temporaries
+        blk = backend.alloc(nbytes)              # first fit would return tmp's block
+        pkg._native.check(pkg._native.lib.fhe_h2d(backend.h, blk, pattern.ctypes.data_as(ctypes.c_void_p), pattern.nbytes, 0))
+        backend.sync()                           # everything, including the pending fills
+        assert np.array_equal(backend.d2h(blk, 4096), pattern), "a freed block was reused while writes to it were pending"
+        backend.free(blk)
+    # a ring created right after such a free uploads its tables with a blocking copy: they must survive too
+    tmp = backend.alloc(nbytes)
+    for k in range(40):
+        ring.fill_uniform(tmp, batch, 2000 + k, stream=3)
+    backend.free(tmp)
+    ring2 = pkg.Ring(backend, n, q, psi)
+    backend.sync()
+    for t in (0, towers - 1):
+        assert np.array_equal(ring2.table(t, 0), ring.table(t, 0))
+    ring2.close()
+    with pytest.raises(pkg.FheError):
+        backend.free(0xdead00)                   # not an arena block
+    p = backend.alloc(256)
+    ring.fill_uniform(p, 0, 1, stream=1)
+    backend.free(p)
+    backend.sync()
+    ring.close()
+
+
+def test_flat_vector_eq_forms_in_place(pkg, backend, oracle):
+    """VECTOR_EQ / SCALAR_EQ descriptor kinds run with dst == a (pim/common.h:14-21)."""
+    q = 1152921504606748673
+    for n in (3, 4097, 100001):
+        rng = np.random.default_rng(n)
+        a = rng.integers(0, q, size=n, dtype=np.uint64)
+        b = rng.integers(0, q, size=n, dtype=np.uint64)
+        da, db = backend.alloc(n * 8), backend.alloc(n * 8)
+        for op in (ADD, SUB, MUL):
+            backend.h2d(da, a); backend.h2d(db, b)
+            backend.vec_op(op, da, da, db, n, q)
+            assert np.array_equal(backend.d2h(da, n), oracle.vec(op, a, b, q))
+            backend.h2d(da, a)
+            backend.vec_op(op, db, da, db, n, q)             # dst == b
+            assert np.array_equal(backend.d2h(db, n), oracle.vec(op, a, b, q))
+            backend.h2d(da, a)
+            backend.vec_op_scalar(op, da, da, 12345678901234567, n, q)
+            assert np.array_equal(backend.d2h(da, n), oracle.vec_scalar(op, a, 12345678901234567, q))
+        backend.free(da); backend.free(db)

@@ -44,7 +44,7 @@ def cpu_bfv(n, sq, sr, pairs, t):
     mk = lambda a, b: H.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
     cQ, cR, cQR = mk(0, sq), mk(sq, sq + sr), mk(0, sq + sr)
     hs = [H.ref_polys_load(cQ, p(O.fill_ring(pairs, n, q[:sq].copy(), 700 + k)), pairs, 0) for k in range(4)]
-    threads = H.ref_max_threads()
+    threads = max(1, len(os.sched_getaffinity(0)))      # not omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1
     best = None
     for _ in range(2):
         outs, sec = (vp * 3)(), ctypes.c_double()

@@ -98,6 +98,7 @@ SIGNATURES = {
 
 FHE_OK, FHE_EINVAL, FHE_ECUDA, FHE_ENOMEM, FHE_ENODEV, FHE_EUNSUPPORTED = 0, -1, -2, -3, -4, -5
 OP_ADD, OP_SUB, OP_MUL = 0, 1, 2
+OP_NTT, OP_INTT = 3, 4          # fhe_dcrt_chain_host only: SwitchFormat forward / inverse
 
 
 class FheError(RuntimeError):

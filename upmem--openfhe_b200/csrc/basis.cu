@@ -434,7 +434,7 @@ cudaError_t launch_scale_round(const ScaleDev& sd, uint64_t* dst, const uint64_t
 //   mode 2 (ModReduce :809-810)           out = (x + v * t) * c
 template <int MODE>
 __global__ void __launch_bounds__(256)
-tower_affine_kernel(u64* __restrict__ out, const u64* __restrict__ x, const u64* __restrict__ v, size_t npairs, u32 logN,
+tower_affine_kernel(u64* out, const u64* x, const u64* v, size_t npairs, u32 logN,
                     u32 l, u32 xT, const TowerMod* __restrict__ mods, const ulonglong4* __restrict__ k) {
     for (size_t p = (size_t)blockIdx.x * 256 + threadIdx.x; p < npairs; p += (size_t)gridDim.x * 256) {
         size_t e = 2 * p;
@@ -458,7 +458,7 @@ tower_affine_kernel(u64* __restrict__ out, const u64* __restrict__ x, const u64*
 
 // scalar form of the same for N = 1 (no aligned pairs)
 template <int MODE>
-__global__ void tower_affine_scalar_kernel(u64* __restrict__ out, const u64* __restrict__ x, const u64* __restrict__ v,
+__global__ void tower_affine_scalar_kernel(u64* out, const u64* x, const u64* v,
                                            size_t total, u32 logN, u32 l, u32 xT, const TowerMod* __restrict__ mods,
                                            const ulonglong4* __restrict__ k) {
     for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
@@ -546,7 +546,7 @@ cudaError_t launch_rescale_spread(uint64_t* tmp, const uint64_t* last, size_t ba
 //          the sum stays below 2^64, and the Shoup product is exact for any 64-bit operand — one product per coefficient
 template <int MODE>
 __global__ void __launch_bounds__(256)
-tower_scale_kernel(u64* __restrict__ out, const u64* __restrict__ x, size_t npairs, u32 logN, u32 sl, u32 T,
+tower_scale_kernel(u64* out, const u64* x, size_t npairs, u32 logN, u32 sl, u32 T,
                    const TowerMod* __restrict__ mods, const ulonglong4* __restrict__ k) {
     const u32 xT = MODE == 0 ? sl : T + 1;
     for (size_t p = (size_t)blockIdx.x * 256 + threadIdx.x; p < npairs; p += (size_t)gridDim.x * 256) {
@@ -589,7 +589,7 @@ tower_scale_kernel(u64* __restrict__ out, const u64* __restrict__ x, size_t npai
 
 // scalar form for N = 1
 template <int MODE>
-__global__ void tower_scale_scalar_kernel(u64* __restrict__ out, const u64* __restrict__ x, size_t batch, u32 sl, u32 T,
+__global__ void tower_scale_scalar_kernel(u64* out, const u64* x, size_t batch, u32 sl, u32 T,
                                           const TowerMod* __restrict__ mods, const ulonglong4* __restrict__ k) {
     const u32 xT = MODE == 0 ? sl : T + 1;
     for (size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x; b < batch; b += (size_t)gridDim.x * blockDim.x)

@@ -45,7 +45,7 @@ constexpr int EW_TILE    = EW_THREADS * EW_UNROLL * 2;     // coefficients per C
 // total = batch*T*N coefficients, nvec = total/2.  UNIFORM: N >= EW_TILE, so a CTA sees one tower.
 template <int OP, bool UNIFORM>
 __global__ void __launch_bounds__(EW_THREADS)
-ew_ring_kernel(u64* __restrict__ dst, const u64* __restrict__ a, const u64* __restrict__ b,
+ew_ring_kernel(u64* dst, const u64* a, const u64* b,
                size_t nvec, u32 logN, u32 T, const TowerMod* __restrict__ mods) {
     const size_t v0 = (size_t)blockIdx.x * (EW_THREADS * EW_UNROLL) + threadIdx.x;
     const ulonglong2* av = reinterpret_cast<const ulonglong2*>(a);
@@ -88,9 +88,7 @@ constexpr int TP_UNROLL  = 2;
 
 template <bool UNIFORM>
 __global__ void __launch_bounds__(TP_THREADS)
-ew_tensor_kernel(u64* __restrict__ c0, u64* __restrict__ c1, u64* __restrict__ c2,
-                 const u64* __restrict__ a0, const u64* __restrict__ a1,
-                 const u64* __restrict__ b0, const u64* __restrict__ b1,
+ew_tensor_kernel(u64* c0, u64* c1, u64* c2, const u64* a0, const u64* a1, const u64* b0, const u64* b1,
                  size_t nvec, u32 logN, u32 T, const TowerMod* __restrict__ mods) {
     const size_t v0 = (size_t)blockIdx.x * (TP_THREADS * TP_UNROLL) + threadIdx.x;
     ulonglong2 xa0[TP_UNROLL], xa1[TP_UNROLL], xb0[TP_UNROLL], xb1[TP_UNROLL];
@@ -157,7 +155,7 @@ cudaError_t launch_tensor_product(const RingDev& r, uint64_t* c0, uint64_t* c1, 
 // SCALAR: second operand is the broadcast value sb.
 template <int OP, bool SCALAR>
 __global__ void __launch_bounds__(256)
-ew_flat_kernel(u64* __restrict__ dst, const u64* __restrict__ a, const u64* __restrict__ b, u64 sb,
+ew_flat_kernel(u64* dst, const u64* a, const u64* b, u64 sb,
                size_t first, size_t n, TowerMod m) {
     size_t i = first + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) dst[i] = ew_apply<OP>(a[i], SCALAR ? sb : b[i], m);
@@ -166,7 +164,7 @@ ew_flat_kernel(u64* __restrict__ dst, const u64* __restrict__ a, const u64* __re
 // Flat vector, 128-bit path (16 B aligned pointers), nvec = n/2.
 template <int OP, bool SCALAR>
 __global__ void __launch_bounds__(EW_THREADS)
-ew_flat_vec_kernel(u64* __restrict__ dst, const u64* __restrict__ a, const u64* __restrict__ b, u64 sb,
+ew_flat_vec_kernel(u64* dst, const u64* a, const u64* b, u64 sb,
                    size_t nvec, TowerMod m) {
     const size_t v0 = (size_t)blockIdx.x * (EW_THREADS * EW_UNROLL) + threadIdx.x;
     const ulonglong2* av = reinterpret_cast<const ulonglong2*>(a);

@@ -35,7 +35,7 @@ __device__ __forceinline__ u64 divround(u64 v, u64 q) {
 
 // kind: enum mod_kernel of pim/common.h.  err: set to 1 when an element has no inverse.
 __global__ void __launch_bounds__(256)
-modop_kernel(int kind, u64* __restrict__ dst, const u64* __restrict__ src, size_t n, u64 mod, u64 p, u64 q,
+modop_kernel(int kind, u64* dst, const u64* src, size_t n, u64 mod, u64 p, u64 q,
              TowerMod tm, int barrett, int* __restrict__ err) {
     const u64 half = mod >> 1;
     const double pd = __ull2double_rn(p), qd = __ull2double_rn(q);

@@ -11,10 +11,12 @@
 #include "serial.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -73,7 +75,8 @@ struct Arena {
         if (bytes == 0) bytes = ARENA_ALIGN;
         bytes = (bytes + ARENA_ALIGN - 1) / ARENA_ALIGN * ARENA_ALIGN;
         std::lock_guard<std::mutex> lk(mu);
-        for (int pass = 0; pass < 2; pass++) {
+        if (!parked.empty()) reap_locked();
+        for (int pass = 0; pass < 3; pass++) {
             for (size_t s = 0; s < slabs.size(); s++) {
                 auto& fl = slabs[s].free_;
                 for (auto it = fl.begin(); it != fl.end(); ++it) {
@@ -87,7 +90,13 @@ struct Arena {
                     return FHE_OK;
                 }
             }
-            if (pass == 1) break;
+            if (pass == 2) break;
+            if (pass == 0) {                       // blocks parked behind unfinished work: wait for it rather than grow
+                if (parked.empty()) continue;
+                cudaDeviceSynchronize();
+                flush_locked();
+                continue;
+            }
             Slab sl;
             sl.size = std::max(slab_bytes, bytes);
             cudaError_t e = cudaMalloc((void**)&sl.base, sl.size);
@@ -103,8 +112,8 @@ struct Arena {
         return fail(FHE_ENOMEM, "device arena: no block of %zu bytes", bytes);
     }
 
-    int release(void* p) {
-        std::lock_guard<std::mutex> lk(mu);
+    // give the block back to the free list NOW (the caller knows no device work can still touch it)
+    int release_locked(void* p) {
         auto it = live.find((uintptr_t)p);
         if (it == live.end()) return fail(FHE_EINVAL, "fhe_free: %p is not a live arena block", p);
         int s = it->second.first;
@@ -121,8 +130,59 @@ struct Arena {
         fl[off] = len;
         return FHE_OK;
     }
+    // ---- stream-ordered release ----------------------------------------------------------------
+    // A released block is parked behind one CUDA event per stream of the context that has carried work since that
+    // stream's last marker (markers are shared between blocks: a stream with no new work costs nothing), and goes
+    // back to the free list only when all of them have completed.  So a temporary may be freed right after the
+    // launches that use it were enqueued, on any stream of the pool or the legacy stream, and a block handed out by
+    // alloc() is never touched by work that was enqueued before it was freed.
+    struct Marker {
+        cudaEvent_t ev = nullptr;
+        bool done = false;
+        bool finished() {
+            if (!done) {
+                cudaError_t e = cudaEventQuery(ev);
+                if (e == cudaSuccess) done = true;
+                else if (e != cudaErrorNotReady) { cudaGetLastError(); done = true; }   // a dead context frees nothing later either
+            }
+            return done;
+        }
+    };
+    struct Parked { void* p; std::vector<std::shared_ptr<Marker>> waits; };
+    std::deque<Parked> parked;
+    std::vector<cudaEvent_t> spare_events;
+    struct StreamMark { std::shared_ptr<Marker> last; uint64_t epoch = 0; };
+    std::vector<StreamMark> marks;                 // one per stream slot (pool streams, then the legacy stream)
+
+    std::shared_ptr<Marker> new_marker(cudaStream_t st) {
+        cudaEvent_t ev = nullptr;
+        if (!spare_events.empty()) { ev = spare_events.back(); spare_events.pop_back(); }
+        else if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        if (cudaEventRecord(ev, st) != cudaSuccess) { cudaGetLastError(); spare_events.push_back(ev); return nullptr; }
+        auto* sp = &spare_events;
+        return std::shared_ptr<Marker>(new Marker{ev, false}, [sp](Marker* m) { sp->push_back(m->ev); delete m; });
+    }
+
+    // blocks whose markers have all completed return to the free list (called with mu held)
+    void reap_locked() {
+        for (auto it = parked.begin(); it != parked.end();) {
+            bool ready = true;
+            for (auto& w : it->waits)
+                if (!w->finished()) { ready = false; break; }
+            if (ready) { release_locked(it->p); it = parked.erase(it); }
+            else ++it;
+        }
+    }
+    void flush_locked() {                          // after a device-wide synchronisation: nothing is pending any more
+        for (auto& pk : parked) release_locked(pk.p);
+        parked.clear();
+    }
 
     void destroy() {
+        parked.clear();
+        marks.clear();
+        for (cudaEvent_t e : spare_events) cudaEventDestroy(e);
+        spare_events.clear();
         for (auto& s : slabs) cudaFree(s.base);
         slabs.clear();
         live.clear();
@@ -137,6 +197,10 @@ struct Timer { cudaEvent_t a = nullptr, b = nullptr; };
 struct fhe_ctx {
     int device = 0;
     std::vector<cudaStream_t> streams;
+    // epoch[slot] counts the API calls that have enqueued work on a stream (slot = pool index; the legacy stream
+    // is the last slot).  It is bumped when such a call returns, so "epoch unchanged since a marker was recorded"
+    // means the marker covers everything the stream carries (Arena::park).
+    std::unique_ptr<std::atomic<uint64_t>[]> epoch;
     Arena arena;
     std::mutex mu;
     std::map<int, Timer> timers;
@@ -159,12 +223,61 @@ struct fhe_ring {
     std::unique_ptr<serial::Layout> layout;
 };
 
-static int get_stream(fhe_ctx* ctx, int stream, cudaStream_t* out) {
+// A stream of the context as an API call uses it: converts to cudaStream_t, and when the call returns (after its
+// launches were enqueued) marks the stream as carrying new work, which is what fhe_free orders itself against.
+struct StreamRef {
+    cudaStream_t st = nullptr;
+    fhe_ctx* ctx = nullptr;
+    int slot = -1;
+    StreamRef() = default;
+    StreamRef(fhe_ctx* c, int pool_index) : st(c->streams[pool_index]), ctx(c), slot(pool_index) {}
+    StreamRef(const StreamRef&) = delete;
+    StreamRef& operator=(const StreamRef&) = delete;
+    operator cudaStream_t() const { return st; }
+    ~StreamRef() { if (ctx && slot >= 0) ctx->epoch[slot].fetch_add(1, std::memory_order_release); }
+};
+
+static int get_stream(fhe_ctx* ctx, int stream, StreamRef* out) {
     if (!ctx) return fail(FHE_EINVAL, "null context");
-    if (stream == FHE_STREAM_LEGACY) { *out = cudaStreamLegacy; return FHE_OK; }
+    if (stream == FHE_STREAM_LEGACY) {
+        out->st = cudaStreamLegacy; out->ctx = ctx; out->slot = (int)ctx->streams.size();
+        return FHE_OK;
+    }
     if (stream < 0 || stream >= (int)ctx->streams.size())
         return fail(FHE_EINVAL, "stream index %d out of range [0,%zu)", stream, ctx->streams.size());
-    *out = ctx->streams[stream];
+    out->st = ctx->streams[stream]; out->ctx = ctx; out->slot = stream;
+    return FHE_OK;
+}
+
+// fhe_free and every internal release of a block that launches may still be using: see Arena::parked.
+static int arena_park(fhe_ctx* ctx, void* p) {
+    if (!p) return FHE_OK;
+    Arena& A = ctx->arena;
+    std::lock_guard<std::mutex> lk(A.mu);
+    if (A.live.find((uintptr_t)p) == A.live.end()) return fail(FHE_EINVAL, "fhe_free: %p is not a live arena block", p);
+    for (auto& pk : A.parked)
+        if (pk.p == p) return fail(FHE_EINVAL, "fhe_free: %p was already freed", p);
+    const size_t nslots = ctx->streams.size() + 1;
+    if (A.marks.size() != nslots) A.marks.resize(nslots);
+    Arena::Parked pk{p, {}};
+    for (size_t i = 0; i < nslots; i++) {
+        uint64_t e = ctx->epoch[i].load(std::memory_order_acquire);
+        if (e == 0) continue;                                   // this stream has never carried work
+        Arena::StreamMark& m = A.marks[i];
+        if (!m.last || m.epoch != e) {
+            auto mk = A.new_marker(i + 1 == nslots ? cudaStreamLegacy : ctx->streams[i]);
+            if (!mk) {                                          // cannot record: fall back to waiting for the device
+                cudaDeviceSynchronize();
+                A.flush_locked();
+                return A.release_locked(p);
+            }
+            m.last = mk; m.epoch = e;
+        }
+        if (!m.last->finished()) pk.waits.push_back(m.last);
+    }
+    if (pk.waits.empty()) return A.release_locked(p);
+    A.parked.push_back(std::move(pk));
+    if (A.parked.size() > 64) A.reap_locked();
     return FHE_OK;
 }
 
@@ -202,6 +315,8 @@ extern "C" int fhe_init(int device, const char* opts, fhe_ctx** out) {
     auto* ctx = new fhe_ctx;
     ctx->device = device;
     long ns = std::max(1l, std::min(64l, opt_value(opts, "streams", 4)));
+    ctx->epoch.reset(new std::atomic<uint64_t>[ns + 1]);
+    for (long i = 0; i <= ns; i++) ctx->epoch[i].store(0);
     ctx->arena.slab_bytes = (size_t)std::max(1l, opt_value(opts, "arena_mb", 256)) << 20;
     ctx->chunk_bytes = (size_t)std::max(1l, std::min(1024l, opt_value(opts, "chunk_mb", 32))) << 20;
     for (long i = 0; i < ns; i++) {
@@ -236,7 +351,7 @@ extern "C" int fhe_sync(fhe_ctx* ctx, int stream) {
     if (!ctx) return fail(FHE_EINVAL, "null context");
     CUDA_TRY(cudaSetDevice(ctx->device));
     if (stream == -2) { CUDA_TRY(cudaDeviceSynchronize()); return FHE_OK; }
-    cudaStream_t s;
+    StreamRef s;
     int rc = get_stream(ctx, stream, &s);
     if (rc) return rc;
     CUDA_TRY(cudaStreamSynchronize(s));
@@ -259,7 +374,8 @@ extern "C" int fhe_alloc(fhe_ctx* ctx, size_t bytes, fhe_dptr* out) {
 extern "C" int fhe_free(fhe_ctx* ctx, fhe_dptr p) {
     if (!ctx) return fail(FHE_EINVAL, "null context");
     if (!p) return FHE_OK;
-    return ctx->arena.release((void*)(uintptr_t)p);
+    cudaSetDevice(ctx->device);
+    return arena_park(ctx, (void*)(uintptr_t)p);
 }
 
 extern "C" int fhe_arena_stats(fhe_ctx* ctx, size_t* reserved_bytes, size_t* in_use_bytes) {
@@ -293,7 +409,7 @@ extern "C" int fhe_host_free(fhe_ctx* ctx, void* p) {
 }
 
 static int copy_async(fhe_ctx* ctx, void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = get_stream(ctx, stream, &s);
     if (rc) return rc;
     if (bytes == 0) return FHE_OK;
@@ -316,7 +432,7 @@ extern "C" int fhe_d2d(fhe_ctx* ctx, fhe_dptr dst, fhe_dptr src, size_t bytes, i
 // timing
 // ---------------------------------------------------------------------------------------------
 extern "C" int fhe_timer_start(fhe_ctx* ctx, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = get_stream(ctx, stream, &s);
     if (rc) return rc;
     CUDA_TRY(cudaSetDevice(ctx->device));
@@ -331,7 +447,7 @@ extern "C" int fhe_timer_start(fhe_ctx* ctx, int stream) {
 }
 
 extern "C" int fhe_timer_stop(fhe_ctx* ctx, int stream, float* elapsed_ms) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = get_stream(ctx, stream, &s);
     if (rc) return rc;
     Timer* t;
@@ -387,10 +503,10 @@ extern "C" int fhe_ring_destroy(fhe_ring* r) {
     fhe_ctx* c = r->ctx;
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
-    if (r->d_mods) c->arena.release(r->d_mods);
-    if (r->d_twF) c->arena.release(r->d_twF);
-    if (r->d_twI) c->arena.release(r->d_twI);
-    if (r->d_invc) c->arena.release(r->d_invc);
+    if (r->d_mods) arena_park(c, r->d_mods);
+    if (r->d_twF) arena_park(c, r->d_twF);
+    if (r->d_twI) arena_park(c, r->d_twI);
+    if (r->d_invc) arena_park(c, r->d_invc);
     delete r;
     return FHE_OK;
 }
@@ -496,7 +612,7 @@ extern "C" int fhe_ring_table(const fhe_ring* r, uint32_t tower, int which, uint
 // ---------------------------------------------------------------------------------------------
 // hot path, device-resident operands
 // ---------------------------------------------------------------------------------------------
-static int ring_stream(fhe_ring* r, int stream, cudaStream_t* s) {
+static int ring_stream(fhe_ring* r, int stream, StreamRef* s) {
     if (!r) return fail(FHE_EINVAL, "null ring");
     int rc = get_stream(r->ctx, stream, s);
     if (rc) return rc;
@@ -505,7 +621,7 @@ static int ring_stream(fhe_ring* r, int stream, cudaStream_t* s) {
 }
 
 extern "C" int fhe_dcrt_op(fhe_ring* r, int op, fhe_dptr dst, fhe_dptr a, fhe_dptr b, size_t batch, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(r, stream, &s);
     if (rc) return rc;
     if (op < FHE_OP_ADD || op > FHE_OP_MUL) return fail(FHE_EINVAL, "fhe_dcrt_op: unknown op %d", op);
@@ -518,7 +634,7 @@ extern "C" int fhe_dcrt_op(fhe_ring* r, int op, fhe_dptr dst, fhe_dptr a, fhe_dp
 }
 
 extern "C" int fhe_ntt_algo(fhe_ring* r, fhe_dptr x, size_t batch, int inverse, int algo, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(r, stream, &s);
     if (rc) return rc;
     if (r->ntt_identity) return FHE_OK;       // psi in {0,1}: the reference returns untouched
@@ -542,7 +658,7 @@ extern "C" int fhe_poly_mul(fhe_ring* r, fhe_dptr c, fhe_dptr a, fhe_dptr b, siz
 }
 
 extern "C" int fhe_automorphism(fhe_ring* r, fhe_dptr dst, fhe_dptr src, size_t batch, uint32_t k, int format, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(r, stream, &s);
     if (rc) return rc;
     if (format != 0 && format != 1) return fail(FHE_EINVAL, "fhe_automorphism: format must be 0 (EVALUATION) or 1 (COEFFICIENT)");
@@ -568,7 +684,7 @@ extern "C" int fhe_precompute_automap(uint32_t N, uint32_t k, uint32_t* map) {
 }
 
 extern "C" int fhe_automorphism_map(fhe_ring* r, fhe_dptr dst, fhe_dptr src, size_t batch, fhe_dptr map, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(r, stream, &s);
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
@@ -581,7 +697,7 @@ extern "C" int fhe_automorphism_map(fhe_ring* r, fhe_dptr dst, fhe_dptr src, siz
 
 extern "C" int fhe_ct_tensor_product(fhe_ring* r, const fhe_dptr* c, const fhe_dptr* a, const fhe_dptr* b,
                                      size_t batch, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(r, stream, &s);
     if (rc) return rc;
     if (!c || !a || !b) return fail(FHE_EINVAL, "fhe_ct_tensor_product: null argument");
@@ -617,7 +733,7 @@ extern "C" int fhe_ct_multiply(fhe_ring* r, const fhe_dptr* c, const fhe_dptr* a
 }
 
 extern "C" int fhe_fill_uniform(fhe_ring* r, fhe_dptr dst, size_t batch, uint64_t seed, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(r, stream, &s);
     if (rc) return rc;
     if (batch && !dst) return fail(FHE_EINVAL, "fhe_fill_uniform: null device pointer");
@@ -637,7 +753,7 @@ static int check_vec_mod(int op, uint64_t q) {
 }
 
 extern "C" int fhe_vec_op(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, fhe_dptr b, size_t n, uint64_t q, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = get_stream(ctx, stream, &s);
     if (rc || (rc = check_vec_mod(op, q))) return rc;
     if (n == 0) return FHE_OK;
@@ -651,7 +767,7 @@ extern "C" int fhe_vec_op(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, fhe_dp
 // methods do it: ModExp reduces the exponent mod the modulus first (mubintvecnat.cpp:391-392).
 extern "C" int fhe_vec_modop(fhe_ctx* ctx, int kind, fhe_dptr dst, fhe_dptr src, size_t n, uint64_t mod,
                              uint64_t p, uint64_t q, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = get_stream(ctx, stream, &s);
     if (rc) return rc;
     if (kind < SWITCHMODULUS || kind > DIVIDEANDROUNDEQ) return fail(FHE_EINVAL, "fhe_vec_modop: unknown mod_kernel %d", kind);
@@ -687,7 +803,7 @@ extern "C" int fhe_vec_modop(fhe_ctx* ctx, int kind, fhe_dptr dst, fhe_dptr src,
 
 extern "C" int fhe_vec_op_scalar(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, uint64_t scalar, size_t n,
                                  uint64_t q, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = get_stream(ctx, stream, &s);
     if (rc || (rc = check_vec_mod(op, q))) return rc;
     if (n == 0) return FHE_OK;
@@ -698,7 +814,7 @@ extern "C" int fhe_vec_op_scalar(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a,
 }
 
 extern "C" int fhe_checksum(fhe_ctx* ctx, fhe_dptr src, size_t nwords, uint64_t* sum_xor, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = get_stream(ctx, stream, &s);
     if (rc) return rc;
     if (!sum_xor) return fail(FHE_EINVAL, "fhe_checksum: null output");
@@ -709,7 +825,7 @@ extern "C" int fhe_checksum(fhe_ctx* ctx, fhe_dptr src, size_t nwords, uint64_t*
     cudaError_t e = launch_checksum((const uint64_t*)(uintptr_t)src, nwords, (uint64_t*)d, s);
     if (e == cudaSuccess) e = cudaMemcpyAsync(sum_xor, d, 16, cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
-    ctx->arena.release(d);
+    arena_park(ctx, d);
     if (e != cudaSuccess) return fail(FHE_ECUDA, "fhe_checksum: %s", cudaGetErrorString(e));
     return FHE_OK;
 }
@@ -784,13 +900,13 @@ struct Scratch {
     size_t bytes = 0;
     int need(fhe_ctx* ctx, size_t n) {
         if (n <= bytes) return FHE_OK;
-        if (p) { cudaDeviceSynchronize(); ctx->arena.release(p); p = nullptr; bytes = 0; }
+        if (p) { cudaDeviceSynchronize(); arena_park(ctx, p); p = nullptr; bytes = 0; }
         int rc = ctx->arena.alloc(n, &p);
         if (rc) return rc;
         bytes = n;
         return FHE_OK;
     }
-    void drop(fhe_ctx* ctx) { if (p) ctx->arena.release(p); p = nullptr; bytes = 0; }
+    void drop(fhe_ctx* ctx) { if (p) arena_park(ctx, p); p = nullptr; bytes = 0; }
 };
 
 template <class T>
@@ -798,6 +914,8 @@ int upload(fhe_ctx* ctx, const std::vector<T>& h, void** d) {
     if (!*d) {
         int rc = ctx->arena.alloc(std::max<size_t>(h.size() * sizeof(T), 16), d);
         if (rc) return rc;
+    } else {
+        cudaDeviceSynchronize();      // a table being replaced may still be read by launches on the (non-blocking) pool streams
     }
     cudaError_t e = cudaMemcpy(*d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
     return e == cudaSuccess ? FHE_OK : fail(FHE_ECUDA, "upload constants: %s", cudaGetErrorString(e));
@@ -861,7 +979,7 @@ extern "C" int fhe_basis_destroy(fhe_basis* b) {
     cudaSetDevice(b->ctx->device);
     cudaDeviceSynchronize();
     for (void* p : {b->d_q, b->d_pre, b->d_hat, b->d_tgt, b->d_pinv, b->d_pre_t, b->d_tgt_t, b->d_qinv, b->d_alphaq})
-        if (p) b->ctx->arena.release(p);
+        if (p) arena_park(b->ctx, p);
     b->s0.drop(b->ctx);
     b->s1.drop(b->ctx);
     delete b;
@@ -924,7 +1042,7 @@ extern "C" int fhe_basis_tables(const fhe_basis* b, uint64_t* qhat_inv_modq, uin
 
 extern "C" int fhe_approx_switch_crt_basis(fhe_basis* b, fhe_dptr dst, fhe_dptr src, size_t batch, int stream) {
     if (!b) return fail(FHE_EINVAL, "null basis");
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(b->from, stream, &s);
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
@@ -962,7 +1080,7 @@ static int ring_ntt(fhe_ring* r, uint64_t* x, size_t batch, bool inverse, cudaSt
 
 extern "C" int fhe_approx_mod_up(fhe_basis* b, fhe_dptr dst_qp, fhe_dptr src_q, size_t batch, int format, int stream) {
     if (!b) return fail(FHE_EINVAL, "null basis");
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(b->from, stream, &s);
     if (rc) return rc;
     if (format != 0 && format != 1) return fail(FHE_EINVAL, "fhe_approx_mod_up: format must be 0 or 1");
@@ -992,7 +1110,7 @@ extern "C" int fhe_approx_mod_up(fhe_basis* b, fhe_dptr dst_qp, fhe_dptr src_q, 
 
 extern "C" int fhe_approx_mod_down(fhe_basis* b, fhe_dptr dst_q, fhe_dptr src_qp, size_t batch, uint64_t t, int stream) {
     if (!b) return fail(FHE_EINVAL, "null basis");
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(b->from, stream, &s);
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
@@ -1055,7 +1173,7 @@ extern "C" int fhe_rescale_destroy(fhe_rescale* p) {
     cudaSetDevice(p->ctx->device);
     cudaDeviceSynchronize();
     for (void* d : {p->d_sw, p->d_k, p->d_kt})
-        if (d) p->ctx->arena.release(d);
+        if (d) arena_park(p->ctx, d);
     p->s0.drop(p->ctx);
     p->s1.drop(p->ctx);
     delete p->rest;
@@ -1113,7 +1231,7 @@ extern "C" int fhe_rescale_tables(const fhe_rescale* p, uint64_t* qlql, uint64_t
 static int rescale_run(fhe_rescale* p, fhe_dptr dst_, fhe_dptr src_, size_t batch, uint64_t t, int format, int stream,
                        const char* who) {
     if (!p) return fail(FHE_EINVAL, "null rescale plan");
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(p->ring, stream, &s);
     if (rc) return rc;
     if (format != 0 && format != 1) return fail(FHE_EINVAL, "%s: format must be 0 or 1", who);
@@ -1185,7 +1303,7 @@ static int basis_exact_ready(fhe_basis* b) {
 
 extern "C" int fhe_switch_crt_basis(fhe_basis* b, fhe_dptr dst, fhe_dptr src, size_t batch, int stream) {
     if (!b) return fail(FHE_EINVAL, "null basis");
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(b->from, stream, &s);
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
@@ -1200,7 +1318,7 @@ extern "C" int fhe_switch_crt_basis(fhe_basis* b, fhe_dptr dst, fhe_dptr src, si
 static int expand_run(fhe_basis* b, fhe_dptr dst_, fhe_dptr src_q, size_t batch, int format, int result_format, int stream,
                       bool reverse, const char* who) {
     if (!b) return fail(FHE_EINVAL, "null basis");
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(b->from, stream, &s);
     if (rc) return rc;
     if ((format != 0 && format != 1) || (result_format != 0 && result_format != 1))
@@ -1250,7 +1368,7 @@ extern "C" int fhe_fast_expand_crt_basis_pl_over_q(fhe_basis* q2pl, fhe_basis* p
     if (q2pl->ctx != pl2ql->ctx || q2pl->from->dev.N != pl2ql->from->dev.N)
         return fail(FHE_EINVAL, "%s: the two bases must share context and ring dimension", who);
     if (q2pl->to->q != pl2ql->from->q) return fail(FHE_EINVAL, "%s: the second basis must start at the first one's target moduli", who);
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(q2pl->from, stream, &s);
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
@@ -1276,7 +1394,7 @@ extern "C" int fhe_tower_scale_destroy(fhe_tower_scale* p) {
     if (!p) return FHE_OK;
     cudaSetDevice(p->ctx->device);
     cudaDeviceSynchronize();
-    if (p->d_k) p->ctx->arena.release(p->d_k);
+    if (p->d_k) arena_park(p->ctx, p->d_k);
     delete p;
     return FHE_OK;
 }
@@ -1304,7 +1422,7 @@ extern "C" int fhe_tower_scale_create(fhe_ring* ring, const uint64_t* c, fhe_tow
 static int tower_scale_run(fhe_tower_scale* p, int mode, uint32_t sl, fhe_dptr dst, fhe_dptr src, size_t batch, int stream,
                            const char* who) {
     if (!p) return fail(FHE_EINVAL, "null tower-scale plan");
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(p->ring, stream, &s);
     if (rc) return rc;
     const uint32_t T = p->ring->dev.T;
@@ -1342,7 +1460,7 @@ extern "C" int fhe_scale_round_destroy(fhe_scale_round* p) {
     cudaSetDevice(p->ctx->device);
     cudaDeviceSynchronize();
     for (void* d : {p->d_frac, p->d_modo, p->d_tgt})
-        if (d) p->ctx->arena.release(d);
+        if (d) arena_park(p->ctx, d);
     delete p;
     return FHE_OK;
 }
@@ -1384,7 +1502,7 @@ extern "C" int fhe_scale_round_create(fhe_ring* ring, uint32_t size_out, int out
 
 extern "C" int fhe_scale_and_round(fhe_scale_round* p, fhe_dptr dst, fhe_dptr src, size_t batch, int stream) {
     if (!p) return fail(FHE_EINVAL, "null scale-and-round plan");
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(p->ring, stream, &s);
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
@@ -1427,8 +1545,8 @@ struct HostPipe {
         return FHE_OK;
     }
     ~HostPipe() {
-        for (void* p : bufA) r->ctx->arena.release(p);
-        for (void* p : bufB) r->ctx->arena.release(p);
+        for (void* p : bufA) arena_park(r->ctx, p);
+        for (void* p : bufB) arena_park(r->ctx, p);
     }
 };
 }  // namespace
@@ -1449,7 +1567,7 @@ extern "C" int fhe_dcrt_multi_op_host(fhe_ring* r, const int* ops, int nops, uin
     int rc = hp.reserve(batch, true);
     if (rc) return rc;
     std::vector<void*> extra;
-    struct Guard { fhe_ring* r; std::vector<void*>& v; ~Guard() { for (void* p : v) r->ctx->arena.release(p); } } guard{r, extra};
+    struct Guard { fhe_ring* r; std::vector<void*>& v; ~Guard() { for (void* p : v) arena_park(r->ctx, p); } } guard{r, extra};
     for (size_t i = 0; i < hp.nslots * (size_t)(nops - 1); i++) {
         void* p = nullptr;
         if ((rc = r->ctx->arena.alloc(hp.chunk_items * hp.item_words * 8, &p))) return rc;
@@ -1459,7 +1577,7 @@ extern "C" int fhe_dcrt_multi_op_host(fhe_ring* r, const int* ops, int nops, uin
     for (size_t b0 = 0; b0 < batch; b0 += hp.chunk_items, k++) {
         size_t items = std::min(hp.chunk_items, batch - b0), words = items * hp.item_words;
         size_t slot = k % hp.nslots;
-        cudaStream_t s = r->ctx->streams[slot];
+        StreamRef s(r->ctx, (int)slot);
         uint64_t* da = (uint64_t*)hp.bufA[slot];
         uint64_t* db = (uint64_t*)hp.bufB[slot];
         CUDA_TRY(cudaMemcpyAsync(da, a + b0 * hp.item_words, words * 8, cudaMemcpyHostToDevice, s));
@@ -1477,24 +1595,33 @@ extern "C" int fhe_dcrt_multi_op_host(fhe_ring* r, const int* ops, int nops, uin
 extern "C" int fhe_dcrt_chain_host(fhe_ring* r, const int* ops, int nops, uint64_t* a, const uint64_t* b, size_t batch) {
     if (!r) return fail(FHE_EINVAL, "null ring");
     if (!ops || nops < 1 || nops > 8) return fail(FHE_EINVAL, "fhe_dcrt_chain_host: need 1..8 ops");
-    for (int i = 0; i < nops; i++)
-        if (ops[i] < FHE_OP_ADD || ops[i] > FHE_OP_MUL) return fail(FHE_EINVAL, "fhe_dcrt_chain_host: unknown op %d", ops[i]);
+    bool any_ntt = false, any_ew = false;
+    for (int i = 0; i < nops; i++) {
+        if (ops[i] < FHE_OP_ADD || ops[i] > FHE_OP_INTT) return fail(FHE_EINVAL, "fhe_dcrt_chain_host: unknown op %d", ops[i]);
+        any_ntt |= ops[i] >= FHE_OP_NTT;
+        any_ew |= ops[i] <= FHE_OP_MUL;
+    }
     if (batch == 0) return FHE_OK;
-    if (!a || !b) return fail(FHE_EINVAL, "fhe_dcrt_chain_host: null host pointer");
+    if (!a || (any_ew && !b)) return fail(FHE_EINVAL, "fhe_dcrt_chain_host: null host pointer");
+    const bool transform = any_ntt && !r->ntt_identity && r->dev.N > 1;   // psi in {0,1}: SwitchFormat leaves the data alone
+    if (transform && !r->has_ntt) return fail(FHE_EINVAL, "fhe_dcrt_chain_host: ring was created without roots of unity");
     CUDA_TRY(cudaSetDevice(r->ctx->device));
-    HostPipe hp(r, true);
-    int rc = hp.reserve(batch, true);
+    HostPipe hp(r, any_ew);
+    int rc = hp.reserve(batch, any_ew);
     if (rc) return rc;
     size_t k = 0;
     for (size_t b0 = 0; b0 < batch; b0 += hp.chunk_items, k++) {
         size_t items = std::min(hp.chunk_items, batch - b0), words = items * hp.item_words;
         size_t slot = k % hp.nslots;
-        cudaStream_t s = r->ctx->streams[slot];
+        StreamRef s(r->ctx, (int)slot);
         uint64_t* da = (uint64_t*)hp.bufA[slot];
-        uint64_t* db = (uint64_t*)hp.bufB[slot];
+        uint64_t* db = any_ew ? (uint64_t*)hp.bufB[slot] : nullptr;
         CUDA_TRY(cudaMemcpyAsync(da, a + b0 * hp.item_words, words * 8, cudaMemcpyHostToDevice, s));
-        CUDA_TRY(cudaMemcpyAsync(db, b + b0 * hp.item_words, words * 8, cudaMemcpyHostToDevice, s));
-        for (int i = 0; i < nops; i++) CUDA_TRY(launch_elementwise(r->dev, ops[i], da, da, db, items, s));
+        if (any_ew) CUDA_TRY(cudaMemcpyAsync(db, b + b0 * hp.item_words, words * 8, cudaMemcpyHostToDevice, s));
+        for (int i = 0; i < nops; i++) {
+            if (ops[i] <= FHE_OP_MUL) CUDA_TRY(launch_elementwise(r->dev, ops[i], da, da, db, items, s));
+            else if (transform) CUDA_TRY(launch_ntt(r->dev, da, items, ops[i] == FHE_OP_INTT, s, 0));
+        }
         CUDA_TRY(cudaMemcpyAsync(a + b0 * hp.item_words, da, words * 8, cudaMemcpyDeviceToHost, s));
     }
     for (size_t i = 0; i < hp.nslots; i++) CUDA_TRY(cudaStreamSynchronize(r->ctx->streams[i]));
@@ -1519,7 +1646,7 @@ extern "C" int fhe_ntt_host(fhe_ring* r, uint64_t* x, size_t batch, int inverse)
     for (size_t b0 = 0; b0 < batch; b0 += hp.chunk_items, k++) {
         size_t items = std::min(hp.chunk_items, batch - b0), words = items * hp.item_words;
         size_t slot = k % hp.nslots;
-        cudaStream_t s = r->ctx->streams[slot];
+        StreamRef s(r->ctx, (int)slot);
         uint64_t* d = (uint64_t*)hp.bufA[slot];
         CUDA_TRY(cudaMemcpyAsync(d, x + b0 * hp.item_words, words * 8, cudaMemcpyHostToDevice, s));
         CUDA_TRY(launch_ntt(r->dev, d, items, inverse != 0, s, 0));
@@ -1587,7 +1714,7 @@ extern "C" int fhe_serial_parse(uint32_t N, uint32_t T, const uint64_t* q, const
 extern "C" size_t fhe_serial_bytes(fhe_ring* r) { return r ? ring_layout(r).bytes : 0; }
 
 extern "C" int fhe_serialize(fhe_ring* r, void* dst_host, fhe_dptr src, size_t batch, int format, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(r, stream, &s);
     if (rc) return rc;
     if (format != 0 && format != 1) return fail(FHE_EINVAL, "fhe_serialize: format must be 0 or 1");
@@ -1606,7 +1733,7 @@ extern "C" int fhe_serialize(fhe_ring* r, void* dst_host, fhe_dptr src, size_t b
 
 extern "C" int fhe_deserialize(fhe_ring* r, fhe_dptr dst, const void* src_host, size_t len, size_t batch, int* format,
                                size_t* consumed, int stream) {
-    cudaStream_t s;
+    StreamRef s;
     int rc = ring_stream(r, stream, &s);
     if (rc) return rc;
     if (consumed) *consumed = 0;
@@ -1643,16 +1770,16 @@ extern "C" int fhe_imad_probe(fhe_ctx* ctx, int blocks, int threads, int iters, 
     void* out = nullptr;
     int rc = ctx->arena.alloc(256, &out);
     if (rc) return rc;
-    cudaStream_t s = ctx->streams[0];
+    StreamRef s(ctx, 0);
     cudaError_t e = launch_imad_probe((uint64_t*)out, blocks, threads, 16, s);   // warm-up
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
-    if (e != cudaSuccess) { ctx->arena.release(out); return fail(FHE_ECUDA, "imad probe: %s", cudaGetErrorString(e)); }
+    if (e != cudaSuccess) { arena_park(ctx, out); return fail(FHE_ECUDA, "imad probe: %s", cudaGetErrorString(e)); }
     rc = fhe_timer_start(ctx, 0);
     if (!rc) {
         e = launch_imad_probe((uint64_t*)out, blocks, threads, iters, s);
         if (e != cudaSuccess) rc = fail(FHE_ECUDA, "imad probe: %s", cudaGetErrorString(e));
     }
     if (!rc) rc = fhe_timer_stop(ctx, 0, elapsed_ms);
-    ctx->arena.release(out);
+    arena_park(ctx, out);
     return rc;
 }
