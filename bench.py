@@ -250,6 +250,12 @@ def main():
     sampler = ClockSampler(local)
     sampler.start()
 
+    # integer-pipe roof, measured before the long loops (the HBM-bound kernels run into the power cap, and a probe
+    # taken right after them sees the lowered clock for a few ms) and again after them; the roof is the better one
+    blocks, threads, iters = 148 * 8, 256, 4096
+    be.imad_probe(blocks, threads, 64)
+    p_cold = min(be.imad_probe(blocks, threads, iters) for _ in range(3))
+
     def step():
         ring.op(ADD, da, da, db, BATCH, 0)          # a += b
         ring.op(MUL, da, da, db, BATCH, 0)          # a *= b
@@ -285,8 +291,10 @@ def main():
     inv_ms = timed(lambda: ring.ntt(da, BATCH, True, 0), reps)
     mul_ms = timed(lambda: ring.op(MUL, da, da, db, BATCH, 0), reps)
     add_ms = timed(lambda: ring.op(ADD, da, da, db, BATCH, 0), reps)
-    blocks, threads, iters = 148 * 8, 256, 4096
-    p_ms = min(be.imad_probe(blocks, threads, iters) for _ in range(3))
+    be.sync()
+    time.sleep(0.2)                                  # let the power governor settle after the HBM-bound loops
+    p_hot = min(be.imad_probe(blocks, threads, iters) for _ in range(5))
+    p_ms = min(p_cold, p_hot)
     shoup_peak = blocks * threads * iters * 8 / (p_ms * 1e-3)
     peaks, peak_src = measured_peaks()
     traffic = {}
@@ -305,7 +313,9 @@ def main():
         "frac": bf / (fwd_ms * 1e-3) / shoup_peak,
         "traffic": traffic.get("ntt_fwd_dram_bytes_per_transform_b1024"),
         "algorithmic_bytes_per_launch": 16 * coeffs, "launch_ms": fwd_ms,
-        "peak_source": "fhe_imad_probe, measured live in this run (148x8 CTAs x 256 threads x 8 chains)",
+        "peak_source": "fhe_imad_probe, measured live in this run (148x8 CTAs x 256 threads x 8 chains), best of a probe "
+                       "before the timed loops and one after them",
+        "probe_ms": {"before": p_cold, "after": p_hot},
         "coeff_per_s": coeffs / (fwd_ms * 1e-3),
         "inverse": {"launch_ms": inv_ms, "achieved": bf / (inv_ms * 1e-3), "frac": bf / (inv_ms * 1e-3) / shoup_peak,
                     "coeff_per_s": coeffs / (inv_ms * 1e-3)},

@@ -143,7 +143,8 @@ int fhe_dcrt_op(fhe_ring* ring, int op, fhe_dptr dst, fhe_dptr a, fhe_dptr b, si
 /* in-place COEFFICIENT -> EVALUATION (bit-reversed order), and back */
 int fhe_ntt_forward(fhe_ring* ring, fhe_dptr x, size_t batch, int stream);
 int fhe_ntt_inverse(fhe_ring* ring, fhe_dptr x, size_t batch, int stream);
-/* same, selecting the kernel family: 0 auto, 1 single-CTA shared-memory kernel (N <= 4096) */
+/* same, selecting the kernel family: 0 auto, 1 single-CTA shared-memory kernel (N <= 4096), 2 one-tile-per-CTA two-pass
+ * kernels, 3 warp-specialised persistent two-pass kernels (N = 2^14..2^16; what auto picks for large batches) */
 int fhe_ntt_algo(fhe_ring* ring, fhe_dptr x, size_t batch, int inverse, int algo, int stream);
 /* c = INTT(NTT(a) .* NTT(b)): negacyclic product of COEFFICIENT-format polynomials; a and b are
  * left in EVALUATION format (they are transformed in place), c may alias neither. */

@@ -453,3 +453,62 @@ def test_flat_vector_eq_forms_in_place(pkg, backend, oracle):
             backend.vec_op_scalar(op, da, da, 12345678901234567, n, q)
             assert np.array_equal(backend.d2h(da, n), oracle.vec_scalar(op, a, 12345678901234567, q))
         backend.free(da); backend.free(db)
+
+
+# ---- the warp-specialised persistent NTT kernels (csrc/ntt_ws.cu), forced with algo = 3 -------------------------
+@pytest.mark.parametrize("logn,towers,batch,nbits", [
+    (14, 2, 1, 60), (14, 3, 8, 60), (14, 2, 13, 48), (14, 4, 200, 60),
+    (15, 2, 1, 60), (15, 3, 9, 60), (15, 2, 64, 33),
+    (16, 1, 1, 60), (16, 2, 7, 60), (16, 3, 16, 60), (16, 2, 41, 21), (16, 30, 8, 60),
+])
+def test_ntt_ws_kernels_vs_oracle(pkg, backend, oracle, logn, towers, batch, nbits):
+    """Every batch size takes the ring of slots through partial groups (batch % 8 != 0), CTAs with fewer tiles than
+    slots, and (batch 200 / 64 / 41) several laps of the ring."""
+    n = 1 << logn
+    q, psi = params(oracle, nbits, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q, psi)
+    rng = np.random.default_rng(100 + logn * 31 + batch)
+    x = rand_polys(rng, batch, n, q)
+    x[0, :, 0] = (q - 1)
+    x[-1, :, -1] = 0
+    x[0, 0, :] = q[0] - 1                      # a whole tower at the top of the range
+    words = ring.words(batch)
+    d = backend.alloc(words * 8)
+    backend.h2d(d, x)
+    ring.ntt(d, batch, False, algo=3)
+    fwd = backend.d2h(d, words).reshape(x.shape)
+    assert np.array_equal(fwd, octx.ntt(x, inverse=False)), "forward"
+    backend.h2d(d, x)                          # the one-tile-per-CTA kernels agree on the same input
+    ring.ntt(d, batch, False, algo=2)
+    assert np.array_equal(backend.d2h(d, words).reshape(x.shape), fwd), "forward, algo 2"
+    ring.ntt(d, batch, True, algo=3)
+    assert np.array_equal(backend.d2h(d, words).reshape(x.shape), x), "round trip"
+    y = rand_polys(rng, batch, n, q)
+    backend.h2d(d, y)
+    ring.ntt(d, batch, True, algo=3)
+    assert np.array_equal(backend.d2h(d, words).reshape(x.shape), octx.ntt(y, inverse=True)), "inverse"
+    backend.free(d)
+    ring.close()
+
+
+def test_ntt_ws_full_size_round_trip_property(pkg, backend, oracle):
+    """BASELINE configs[2] ring at a batch the default dispatch sends to the persistent kernels: forward then inverse
+    is the identity, and the forward result equals the one-tile-per-CTA kernels' (which the oracle pins at small batch)."""
+    n, towers, batch = 1 << 16, 30, 64
+    q, psi = params(oracle, 60, n, towers)
+    ring = pkg.Ring(backend, n, q, psi)
+    words = ring.words(batch)
+    a, b = backend.alloc(words * 8), backend.alloc(words * 8)
+    ring.fill_uniform(a, batch, 424242)
+    backend.d2d(b, a, words * 8)
+    before = backend.checksum(a, words)
+    ring.ntt(a, batch, False)                  # auto -> persistent kernels
+    ring.ntt(b, batch, False, algo=2)
+    assert backend.checksum(a, words) == backend.checksum(b, words)
+    assert np.array_equal(backend.d2h(a, 1 << 20), backend.d2h(b, 1 << 20))
+    ring.ntt(a, batch, True)
+    ring.ntt(b, batch, True, algo=2)
+    assert backend.checksum(a, words) == before and backend.checksum(b, words) == before
+    backend.free(a); backend.free(b)
+    ring.close()

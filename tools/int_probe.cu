@@ -10,9 +10,11 @@ typedef unsigned long long u64;
 typedef unsigned int u32;
 constexpr int ILP = 8;
 
-enum { K_MADLO, K_MADWIDE, K_MADHI, K_MULHI64, K_MULLO64, K_SHOUP, K_SHOUP_APPROX, K_IADD3, K_COUNT };
+enum { K_MADLO, K_MADWIDE, K_MADHI, K_MULHI64, K_MULLO64, K_SHOUP, K_SHOUP_APPROX, K_IADD3, K_MULWIDE, K_MADWIDE_IND, K_MULHI, K_BFLY, K_COUNT };
 static const char* names[] = {"mad.lo.u32", "mad.wide.u32", "mad.hi.u32", "__umul64hi", "mul.lo.u64 (+add)",
-                              "shoup_lazy (mulhi64 + 2 mullo64)", "shoup_approx (3-product hi)", "add.u32 x3 (alu)"};
+                              "shoup_lazy (mulhi64 + 2 mullo64)", "shoup_approx (3-product hi)", "add.u32 x3 (alu)",
+                              "mul.wide.u32 (no addend)", "mad.wide.u32 (addend not from the multiplier chain)", "mul.hi.u32 (no addend)",
+                              "NTT butterfly multiplier as the kernels write it (2 mul.hi + 3 wide + 4 mad.lo)"};
 
 template <int K>
 __global__ void __launch_bounds__(256) probe(u64* out, int iters, u32 seed) {
@@ -33,6 +35,26 @@ __global__ void __launch_bounds__(256) probe(u64* out, int iters, u32 seed) {
                 u32 y0 = (u32)x[k], y1 = (u32)(x[k] >> 32), p0 = (u32)wp, p1 = (u32)(wp >> 32);
                 u64 qh = (u64)y1 * p1 + __umulhi(y1, p0) + __umulhi(y0, p1);
                 x[k] = x[k] * w + qh * nq;
+            }
+            if (K == K_MULWIDE) x[k] = (u64)(u32)x[k] * (u64)b;
+            if (K == K_MADWIDE_IND) { u64 t = (u64)a[k] * (u64)b + x[k]; x[k] = t; a[k] = (u32)t ^ c; }
+            if (K == K_MULHI) asm volatile("mul.hi.u32 %0, %0, %1;" : "+r"(a[k]) : "r"(b));
+            if (K == K_BFLY) {
+                u32 x0 = (u32)x[k], x1 = (u32)(x[k] >> 32), w0 = (u32)w, w1 = (u32)(w >> 32);
+                u32 p0 = (u32)wp, p1 = (u32)(wp >> 32), n0 = (u32)nq, n1 = (u32)(nq >> 32), t1, t2, lo, hi;
+                asm("mul.hi.u32 %0, %1, %2;" : "=r"(t1) : "r"(x1), "r"(p0));
+                asm("mul.hi.u32 %0, %1, %2;" : "=r"(t2) : "r"(x0), "r"(p1));
+                u64 qh = (u64)t1 + (u64)t2, acc;
+                asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(qh) : "r"(x1), "r"(p1));
+                u32 h0 = (u32)qh, h1 = (u32)(qh >> 32);
+                asm("mul.wide.u32 %0, %1, %2;" : "=l"(acc) : "r"(x0), "r"(w0));
+                asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(h0), "r"(n0));
+                asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(acc));
+                asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(x0), "r"(w1));
+                asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(x1), "r"(w0));
+                asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(h0), "r"(n1));
+                asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(h1), "r"(n0));
+                asm("mov.b64 %0, {%1, %2};" : "=l"(x[k]) : "r"(lo), "r"(hi));
             }
             if (K == K_IADD3) asm volatile("add.u32 %0, %0, %1; add.u32 %0, %0, %2; add.u32 %0, %0, %1;" : "+r"(a[k]) : "r"(b), "r"(c));
         }
@@ -74,6 +96,10 @@ int main(int argc, char** argv) {
     run<K_SHOUP>(d, blocks, iters);
     run<K_SHOUP_APPROX>(d, blocks, iters);
     run<K_IADD3>(d, blocks, iters);
+    run<K_MULWIDE>(d, blocks, iters);
+    run<K_MADWIDE_IND>(d, blocks, iters);
+    run<K_MULHI>(d, blocks, iters);
+    run<K_BFLY>(d, blocks, iters);
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { printf("cuda error %s\n", cudaGetErrorString(e)); return 1; }
     return 0;

@@ -34,12 +34,18 @@ cudaError_t launch_vec(int op, uint64_t* dst, const uint64_t* a, const uint64_t*
 cudaError_t launch_vec_scalar(int op, uint64_t* dst, const uint64_t* a, uint64_t s, size_t n,
                               uint64_t q, cudaStream_t st);
 // Forward / inverse negacyclic NTT of every tower of every batch item, result in data.
-// algo: 0 = auto, 1 = force the single-CTA shared-memory kernel (N <= 4096).
+// algo: 0 = auto, 1 = force the single-CTA shared-memory kernel (N <= 4096), 2 = one-tile-per-CTA kernels (ntt.cu) even
+// where the persistent ones (ntt_ws.cu) would be chosen, 3 = the persistent ones wherever they cover the ring.
 // src: buffer the transform reads (nullptr = data, in place).  outT / inT: towers per batch item in the memory of data /
 // src (0 = r.T): the r.T towers transformed are the first ones of each item, so a pointer offset by t0 * N transforms
 // towers t0 .. t0 + r.T - 1 of a wider poly in place.
 cudaError_t launch_ntt(const RingDev& r, uint64_t* data, size_t batch, bool inverse,
                        cudaStream_t st, int algo, const uint64_t* src = nullptr, uint32_t outT = 0, uint32_t inT = 0);
+// The warp-specialised persistent form of the same transform (ntt_ws.cu; N = 2^14..2^16, large batches); launch_ntt
+// dispatches to it when ntt_ws_applies().
+bool ntt_ws_applies(const RingDev& r, size_t batch);
+cudaError_t launch_ntt_ws(const RingDev& r, uint64_t* data, size_t batch, bool inverse, cudaStream_t st,
+                          const uint64_t* in, uint32_t outT, uint32_t inT);
 // dst = automorphism X -> X^k of src over [batch][T][N] (k odd, dst != src).  format 0 EVALUATION, 1 COEFFICIENT.
 cudaError_t launch_automorphism(const RingDev& r, uint64_t* dst, const uint64_t* src, size_t batch, uint32_t k,
                                 int format, cudaStream_t st);
