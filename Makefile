@@ -17,13 +17,17 @@ $(LIBDIR)/obj/%.o: $(CSRC)/%.cu $(HDR)
 	@mkdir -p $(dir $@)
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 $(LIBDIR)/libfhe_b200.so: $(OBJ)
-	$(NVCC) -gencode arch=compute_100a,code=sm_100a -shared -o $@ $^
+	$(NVCC) -gencode arch=compute_100a,code=sm_100a -shared -o $@ $^ -ldl
 oracle:
 	$(MAKE) -C oracle oracle
 ref:
 	$(MAKE) -C oracle ref
 # C++ parity test of the include/pim surface (links the product .so and, as its checker, the oracle)
-host: lib oracle tests/cpp/bin/pim_surface_test
+host: lib oracle tests/cpp/bin/pim_surface_test tests/cpp/bin/pim_multi_gpu_test
+tests/cpp/bin/pim_multi_gpu_test: tests/cpp/pim_multi_gpu_test.cpp $(HDR)
+	@mkdir -p $(dir $@)
+	g++ -std=c++17 -O2 -Wall -Iinclude -Ioracle $< -o $@ -L$(LIBDIR) -lfhe_b200 -Loracle -lfhe_oracle \
+	    -Wl,-rpath,'$$ORIGIN/../../../$(LIBDIR)' -Wl,-rpath,'$$ORIGIN/../../../oracle'
 tests/cpp/bin/pim_surface_test: tests/cpp/pim_surface_test.cpp $(HDR)
 	@mkdir -p $(dir $@)
 	g++ -std=c++17 -O2 -Wall -Iinclude -Ioracle $< -o $@ -L$(LIBDIR) -lfhe_b200 -Loracle -lfhe_oracle \

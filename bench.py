@@ -223,11 +223,95 @@ def host_mem_available():
     return avail
 
 
+def run_group(args):
+    """`--gpus N` without torchrun: ONE process drives N devices through the library's group API (fhe_group_*), the
+    form a C++ caller of PimManager("gpus=N") gets.  Same step, same metric; device time = max over the devices."""
+    host_threads, omp_was = claim_host_threads()
+    pkg = importlib.import_module("upmem--openfhe_b200")
+    n = args.gpus
+    g = pkg.Group(n, opts="streams=4,arena_mb=1024")
+    q, psi = pkg.gen_params(NBITS, N_RING, TOWERS)
+    ring = pkg.GroupRing(g, N_RING, q, psi)
+    batch = BATCH * n
+    bes = [g.backend(r) for r in range(n)]
+    da, db = ring.alloc(batch), ring.alloc(batch)
+    ring.fill_uniform(da, batch, 20260002)
+    ring.fill_uniform(db, batch, 20261002)
+    g.sync()
+    ADD, MUL = pkg.OP_ADD, pkg.OP_MUL
+    warmup = max(args.warmup, 3)
+    sampler = ClockSampler(0)
+    sampler.start()
+
+    def step():
+        ring.op(ADD, da, da, db, batch)
+        ring.op(MUL, da, da, db, batch)
+        ring.ntt(da, batch, True)
+        ring.ntt(da, batch, False)
+
+    for _ in range(warmup):
+        step()
+    g.sync()
+    l0 = pkg._native.lib.fhe_launch_count()
+    for be in bes:
+        be.timer_start(0)
+    for _ in range(args.steps):
+        step()
+    ms = max(be.timer_stop(0) for be in bes)
+    launches = pkg._native.lib.fhe_launch_count() - l0
+    words = ring.words(batch)
+    value = OPS_PER_SLOT * words * args.steps / (ms * 1e-3)
+    # end to end on host operands: every device streams its block of the pinned host batch through its own pipeline
+    avail = host_mem_available()
+    e2e_batch = batch
+    while e2e_batch > 32 * n and avail is not None and 2 * e2e_batch * TOWERS * N_RING * 8 > 0.4 * avail:
+        e2e_batch //= 2
+    e2e_words = e2e_batch * TOWERS * N_RING
+    ha, pa = bes[0].host_alloc(e2e_words)
+    hb, pb = bes[0].host_alloc(e2e_words)
+    seed_ring = pkg.Ring(bes[0], N_RING, q, psi)
+    tmp = bes[0].alloc(64 * TOWERS * N_RING * 8)
+    for off in range(0, e2e_batch, 64):                 # synthetic residues, 64 polynomials at a time
+        cnt = min(64, e2e_batch - off)
+        for hbuf, sd in ((ha, 1), (hb, 2)):
+            seed_ring.fill_uniform(tmp, cnt, 20260002 + 1000 * sd + off)
+            bes[0].d2h(tmp, cnt * TOWERS * N_RING, out=hbuf[off * TOWERS * N_RING:(off + cnt) * TOWERS * N_RING])
+    bes[0].free(tmp)
+    seed_ring.close()
+    OPS = [ADD, MUL, pkg.OP_INTT, pkg.OP_NTT]
+    ring.chain_host(OPS, ha, hb, e2e_batch)
+    e2e_steps = max(2, min(args.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ring.chain_host(OPS, ha, hb, e2e_batch)
+    e2e_s = time.perf_counter() - t0
+    sampler.stop_flag = True
+    sampler.join()
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n, "steps": args.steps, "warmup": warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+        "data": "synthetic", "config": CONFIG,
+        "parallelism": f"ONE process, {n} devices through fhe_group_* (what PimManager(\"gpus={n}\") drives), batch-sharded, "
+                       "no data-path collective",
+        "roofline": None, "cpu_baseline": None,
+        "e2e": {"value": OPS_PER_SLOT * e2e_words * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 2 * e2e_words * 8,
+                "d2h_bytes_per_step": e2e_words * 8, "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
+                "batch_total": e2e_batch, "api": "fhe_group_chain_host(ADD, MUL, INTT, NTT): one host thread per device"},
+        "gpu_launches": int(launches), "clocks": sampler.summary(),
+    }
+    emit(line)
+    ring.free(da); ring.free(db)
+    ring.close()
+    g.close()
+
+
 def main():
     args = parse()
     claim_stdout()
     if args.impl == "reference":
         return run_reference(args)
+    if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        return run_group(args)
     host_threads, omp_was = claim_host_threads()
     world, rank, local, dist = dist_setup(args.gpus)
     pkg = importlib.import_module("upmem--openfhe_b200")
@@ -383,31 +467,32 @@ def main():
     # 64-polynomial block (1 GB) of every rank's result, HBM to HBM; device-timed on torch's stream, max over ranks ----
     gather = None
     if dist is not None:
-        import torch
         g_batch = 64
         g_words = g_batch * TOWERS * N_RING
         be.sync()
-        dev = torch.device("cuda", local)
-        g = sharding.gather_device(da, g_words, dist, dev)           # warm-up: NCCL channels, output allocation
-        torch.cuda.synchronize()
-        own = g[rank, :4096].cpu().numpy().view("uint64")
+        ids = [pkg.Comm.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)                       # torch carries the 128-byte id, nothing else
+        comm = pkg.Comm(be, world, rank, ids[0])                     # ncclCommInitRank inside libfhe_b200.so
+        gbuf = be.alloc(world * g_words * 8)
+        comm.all_gather(gbuf, da, g_words, 0)                        # warm-up: NCCL channels
+        be.sync()
+        own = be.d2h(gbuf + rank * g_words * 8, 4096)
         assert (own == be.d2h(da, 4096)).all(), "gathered block differs from this rank's result"
         for _ in range(2):                                            # NCCL sets its channels up lazily
-            g = sharding.gather_device(da, g_words, dist, dev, out=g)
-        torch.cuda.synchronize()
+            comm.all_gather(gbuf, da, g_words, 0)
+        be.sync()
         reps_g, rounds = 5, []
         for _ in range(3):                                            # best of three rounds, each max over ranks
             barrier(dist, local)
-            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            ev0.record()
+            be.timer_start(0)
             for _ in range(reps_g):
-                g = sharding.gather_device(da, g_words, dist, dev, out=g)       # the output buffer is reused
-            ev1.record()
-            torch.cuda.synchronize()
-            rounds.append(max_over_ranks(dist, local, ev0.elapsed_time(ev1) / reps_g))
-        del g
+                comm.all_gather(gbuf, da, g_words, 0)
+            rounds.append(max_over_ranks(dist, local, be.timer_stop(0) / reps_g))
+        be.free(gbuf)
+        comm.close()
         g_ms = min(rounds)
-        gather = {"what": f"all_gather_into_tensor of a {g_batch}-polynomial block of each rank's result (NCCL over NVLink/NVSwitch)",
+        gather = {"what": f"fhe_comm_all_gather (ncclAllGather on the library's own stream, NVLink/NVSwitch) of a {g_batch}-polynomial "
+                          "block of each rank's result",
                   "bytes_per_rank": g_words * 8, "ms": g_ms, "rounds_ms": rounds,
                   "recv_gbs_per_rank": (world - 1) * g_words * 8 / (g_ms * 1e-3) / 1e9,
                   "note": "results stay sharded (a full gather is 16.1 GB per rank); value excludes the gather"}

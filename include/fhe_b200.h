@@ -335,6 +335,55 @@ int fhe_dcrt_chain_host(fhe_ring* ring, const int* ops, int nops, uint64_t* a, c
 /* in-place transform of a host buffer (inverse = 0 forward, 1 inverse). Blocking. */
 int fhe_ntt_host(fhe_ring* ring, uint64_t* x, size_t batch, int inverse);
 
+/* ---- several devices of one node ----------------------------------------------- */
+/* The reference scatters a vector over `nr_dpus` DPUs (PimManager::copy_to_pim, src/core/pim/host/PimManager.cpp:15-24:
+ * size / nr_dpus words each) and launches the same kernel on all of them (PimManager.h:68).  Here a group is `ndev`
+ * GPUs driven by one process: one context per device, the batch split in contiguous blocks (sizes differing by at most
+ * one polynomial, the first ranks take the remainder), the ring's tables replicated on every device, no collective
+ * inside the path.  NCCL (libnccl.so.2, loaded at run time) is used only by the gathers below, on this library's own
+ * streams.  Every array argument below has one entry per device of the group, in rank order. */
+typedef struct fhe_group fhe_group;
+typedef struct fhe_group_ring fhe_group_ring;
+/* devices NULL: 0..ndev-1; ndev 0: every visible device.  opts as fhe_init. */
+int fhe_group_create(int ndev, const int* devices, const char* opts, fhe_group** out);
+int fhe_group_destroy(fhe_group* group);
+int fhe_group_size(const fhe_group* group);
+fhe_ctx* fhe_group_ctx(fhe_group* group, int rank);
+int fhe_group_sync(fhe_group* group);                       /* every device */
+/* the block of a batch that `rank` owns: items [*first, *first + *count) */
+int fhe_group_partition(const fhe_group* group, size_t batch, int rank, size_t* first, size_t* count);
+/* fhe_launch on every device at once (PimManager::start_kernel with several devices): the descriptor's sizes are per
+ * device, as PimData computes them (pim/PimData.h:281-290), heap_bases[rank] is that device's heap.  Blocking. */
+int fhe_group_launch(fhe_group* group, int kernel_id, const void* desc, const fhe_dptr* heap_bases);
+int fhe_group_ring_create(fhe_group* group, uint32_t N, uint32_t towers, const uint64_t* q, const uint64_t* psi,
+                          fhe_group_ring** out);
+int fhe_group_ring_destroy(fhe_group_ring* ring);
+fhe_ring* fhe_group_ring_at(fhe_group_ring* ring, int rank); /* the ring on one device, for every single-device call */
+/* one buffer per device, sized for its block of `batch` polynomials */
+int fhe_group_alloc(fhe_group_ring* ring, size_t batch, fhe_dptr* out);
+int fhe_group_free(fhe_group_ring* ring, const fhe_dptr* bufs);
+/* host [batch][T][N] <-> the devices' blocks (asynchronous with pinned host memory; fhe_group_sync completes them) */
+int fhe_group_scatter(fhe_group_ring* ring, const fhe_dptr* dst, const uint64_t* host, size_t batch, int stream);
+int fhe_group_gather(fhe_group_ring* ring, uint64_t* host, const fhe_dptr* src, size_t batch, int stream);
+/* fhe_dcrt_op / fhe_ntt_forward|inverse on every device's block, launched back to back (the devices run concurrently) */
+int fhe_group_dcrt_op(fhe_group_ring* ring, int op, const fhe_dptr* dst, const fhe_dptr* a, const fhe_dptr* b,
+                      size_t batch, int stream);
+int fhe_group_ntt(fhe_group_ring* ring, const fhe_dptr* x, size_t batch, int inverse, int stream);
+/* north_star's "NCCL over NVLink only to gather results": dst[rank] (batch polynomials each) receives every device's
+ * block, HBM to HBM (ncclAllGather, or grouped ncclSend / ncclRecv when the blocks differ in size).  Asynchronous. */
+int fhe_group_all_gather(fhe_group_ring* ring, const fhe_dptr* dst, const fhe_dptr* src, size_t batch, int stream);
+/* fhe_dcrt_chain_host over all devices: each streams its block of the host batch through its own pipeline. Blocking. */
+int fhe_group_chain_host(fhe_group_ring* ring, const int* ops, int nops, uint64_t* a, const uint64_t* b, size_t batch);
+
+/* One rank of a NCCL communicator on a context's device, for one-process-per-GPU callers (torchrun): rank 0 calls
+ * fhe_comm_unique_id (128 bytes) and hands the id to the other ranks by any means; every rank then calls
+ * fhe_comm_create.  fhe_comm_all_gather: dst (nranks * words) receives every rank's `words` words, on `stream`. */
+typedef struct fhe_comm fhe_comm;
+int fhe_comm_unique_id(void* id, size_t cap);
+int fhe_comm_create(fhe_ctx* ctx, int nranks, int rank, const void* id, fhe_comm** out);
+int fhe_comm_destroy(fhe_comm* comm);
+int fhe_comm_all_gather(fhe_comm* comm, fhe_dptr dst, fhe_dptr src, size_t words, int stream);
+
 /* ---- diagnostics ---------------------------------------------------------------------------- */
 /* integer-pipe probe: launches blocks x threads, each thread doing iters x 8 lazy Shoup products
  * (mulhi64 + 2 mullo64 = the multiply work of one NTT butterfly); returns the kernel time so the

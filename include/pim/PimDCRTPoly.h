@@ -14,6 +14,12 @@
  *   ApproxSwitchCRTBasis / ApproxModUp / ApproxModDown      dcrtpoly-impl.h:1034-1175
  *   DropLastElementAndScale / ModReduce                     dcrtpoly-impl.h:746-812
  * Layout in HBM: [batch][tower][N] uint64.  Header only; link with libfhe_b200.so.
+ *
+ * Several GPUs (PimManager with `gpus=k`): a PimRing then holds the ring's tables on every device and a PimDCRTPoly
+ * holds one block of the batch per device (contiguous blocks, fhe_group_partition).  The hot-path methods — construction
+ * from / sync to host data, copy, Plus / Minus / Times, += -= *=, SwitchFormat / SetFormat — run on all devices at once,
+ * with no exchange between them; AllGather() is the optional NCCL gather of a result.  The methods beside
+ * the path (automorphism, basis conversion, rescale, wire format) need a single-device manager and say so.
  */
 #ifndef _PIM_DCRT_POLY_
 #define _PIM_DCRT_POLY_
@@ -38,15 +44,19 @@ public:
   PimRing(PimManager *pim, uint32_t N, const std::vector<uint64_t> &q, const std::vector<uint64_t> &psi)
       : pim_(pim), n_(N), q_(q), psi_(psi) {
     if (!psi.empty() && psi.size() != q.size()) throw pim_math_error("PimRing: one root of unity per modulus");
-    PimManager::check(fhe_ring_create(pim->context(), N, (uint32_t)q.size(), q_.data(),
-                                      psi_.empty() ? nullptr : psi_.data(), &ring_), "PimRing");
+    PimManager::check(fhe_group_ring_create(pim->group(), N, (uint32_t)q.size(), q_.data(),
+                                            psi_.empty() ? nullptr : psi_.data(), &gring_), "PimRing");
+    ring_ = fhe_group_ring_at(gring_, 0);
   }
   /* towers [first, first+count) of `parent`, sharing its device tables (the ILDCRTParams of a sub-basis) */
   static std::shared_ptr<PimRing> View(const std::shared_ptr<PimRing> &parent, uint32_t first, uint32_t count) {
     std::shared_ptr<PimRing> v(new PimRing(parent, first, count));
     return v;
   }
-  ~PimRing() { fhe_ring_destroy(ring_); }
+  ~PimRing() {
+    if (gring_) fhe_group_ring_destroy(gring_);      /* owns the per-device rings */
+    else fhe_ring_destroy(ring_);                    /* a view: only the handle */
+  }
   PimRing(const PimRing &) = delete;
   PimRing &operator=(const PimRing &) = delete;
 
@@ -61,12 +71,15 @@ public:
   size_t GetNumTowers() const { return q_.size(); }
   const std::vector<uint64_t> &GetModuli() const { return q_; }
   const std::vector<uint64_t> &GetRoots() const { return psi_; }
-  fhe_ring *handle() const { return ring_; }
+  fhe_ring *handle() const { return ring_; }                      /* the ring on the first device */
+  fhe_group_ring *group_handle() const { return gring_; }        /* every device's (null for a view) */
+  uint32_t devices() const { return pim_->devices(); }
   PimManager *manager() const { return pim_; }
 
 private:
   PimRing(const std::shared_ptr<PimRing> &parent, uint32_t first, uint32_t count)
       : pim_(parent->pim_), n_(parent->n_), parent_(parent) {
+    if (pim_->devices() > 1) throw pim_not_implemented_error("PimRing::View needs a single-device PimManager");
     PimManager::check(fhe_ring_view(parent->ring_, first, count, &ring_), "PimRing::View");
     q_.assign(parent->q_.begin() + first, parent->q_.begin() + first + count);
     if (!parent->psi_.empty()) psi_.assign(parent->psi_.begin() + first, parent->psi_.begin() + first + count);
@@ -75,6 +88,7 @@ private:
   uint32_t n_;
   std::vector<uint64_t> q_, psi_;
   fhe_ring *ring_ = nullptr;
+  fhe_group_ring *gring_ = nullptr;
   std::shared_ptr<PimRing> parent_;   /* keeps the owner of the tables alive */
 };
 
@@ -171,41 +185,70 @@ public:
   PimDCRTPoly(std::shared_ptr<PimRing> ring, size_t batch, PimFormat format, const uint64_t *host = nullptr,
               int stream = 0)
       : ring_(std::move(ring)), batch_(batch), format_(format), stream_(stream) {
-    PimManager::check(fhe_alloc(ctx(), bytes() ? bytes() : 8, &d_), "PimDCRTPoly");
+    allocate();
     if (host) {
-      PimManager::check(fhe_h2d(ctx(), d_, host, bytes(), stream_), "PimDCRTPoly upload");
-      PimManager::check(fhe_sync(ctx(), stream_), "PimDCRTPoly upload");
+      if (multi()) PimManager::check(fhe_group_scatter(ring_->group_handle(), dv_.data(), host, batch_, stream_), "PimDCRTPoly upload");
+      else PimManager::check(fhe_h2d(ctx(), d_, host, bytes(), stream_), "PimDCRTPoly upload");
+      sync_streams("PimDCRTPoly upload");
     }
   }
   PimDCRTPoly(const PimDCRTPoly &o) : PimDCRTPoly(o.ring_, o.batch_, o.format_, nullptr, o.stream_) {
-    PimManager::check(fhe_d2d(ctx(), d_, o.d_, bytes(), stream_), "PimDCRTPoly copy");
+    for (uint32_t i = 0; i < devices(); i++)
+      PimManager::check(fhe_d2d(ctx(i), ptr(i), o.ptr(i), block_bytes(i), stream_), "PimDCRTPoly copy");
   }
   PimDCRTPoly(PimDCRTPoly &&o) noexcept
-      : ring_(std::move(o.ring_)), batch_(o.batch_), format_(o.format_), stream_(o.stream_), d_(o.d_) { o.d_ = 0; }
+      : ring_(std::move(o.ring_)), batch_(o.batch_), format_(o.format_), stream_(o.stream_), d_(o.d_), dv_(std::move(o.dv_)) {
+    o.d_ = 0;
+    o.dv_.clear();
+  }
   PimDCRTPoly &operator=(PimDCRTPoly o) {
     std::swap(ring_, o.ring_); std::swap(batch_, o.batch_); std::swap(format_, o.format_);
-    std::swap(stream_, o.stream_); std::swap(d_, o.d_);
+    std::swap(stream_, o.stream_); std::swap(d_, o.d_); std::swap(dv_, o.dv_);
     return *this;
   }
-  ~PimDCRTPoly() { if (d_ && ring_) fhe_free(ctx(), d_); }
+  ~PimDCRTPoly() {
+    if (!ring_) return;
+    if (!dv_.empty()) fhe_group_free(ring_->group_handle(), dv_.data());
+    else if (d_) fhe_free(ctx(), d_);
+  }
 
   PimFormat GetFormat() const { return format_; }
   size_t GetBatch() const { return batch_; }
   size_t words() const { return batch_ * ring_->GetNumTowers() * ring_->GetRingDimension(); }
   size_t bytes() const { return words() * sizeof(uint64_t); }
-  fhe_dptr device_ptr() const { return d_; }
+  fhe_dptr device_ptr() const { return d_; }                       /* the block on the first device */
+  fhe_dptr device_ptr(uint32_t rank) const { return ptr(rank); }
+  uint32_t devices() const { return ring_->devices(); }
+  /* polynomials [first, first + count) of the batch live on device `rank` */
+  void GetBlock(uint32_t rank, size_t *first, size_t *count) const {
+    PimManager::check(fhe_group_partition(ring_->manager()->group(), batch_, (int)rank, first, count), "GetBlock");
+  }
   const std::shared_ptr<PimRing> &GetParams() const { return ring_; }
 
   /* device -> host, blocking (the PimData::sync of this handle) */
   void sync(uint64_t *out) const {
-    PimManager::check(fhe_d2h(ctx(), out, d_, bytes(), stream_), "PimDCRTPoly::sync");
-    PimManager::check(fhe_sync(ctx(), stream_), "PimDCRTPoly::sync");
+    if (multi()) PimManager::check(fhe_group_gather(ring_->group_handle(), out, dv_.data(), batch_, stream_), "PimDCRTPoly::sync");
+    else PimManager::check(fhe_d2h(ctx(), out, d_, bytes(), stream_), "PimDCRTPoly::sync");
+    sync_streams("PimDCRTPoly::sync");
   }
   std::vector<uint64_t> GetValues() const { std::vector<uint64_t> v(words()); sync(v.data()); return v; }
+
+  /* north_star's optional gather: every device receives the whole batch, HBM to HBM over NVLink (NCCL on the
+   * library's own streams).  Returns one device pointer per device (batch polynomials each); the caller frees them
+   * with fhe_free on context(rank).  Complete after manager()->sync(). */
+  std::vector<fhe_dptr> AllGather() const {
+    std::vector<fhe_dptr> out(devices(), 0);
+    for (uint32_t i = 0; i < devices(); i++) PimManager::check(fhe_alloc(ctx(i), bytes() ? bytes() : 8, &out[i]), "AllGather");
+    std::vector<fhe_dptr> src(devices());
+    for (uint32_t i = 0; i < devices(); i++) src[i] = ptr(i);
+    PimManager::check(fhe_group_all_gather(ring_->group_handle(), out.data(), src.data(), batch_, stream_), "AllGather");
+    return out;
+  }
 
   /* Wire format: `batch` consecutive streams, each what Serial::Serialize(poly, os, SerType::BINARY) writes for the
    * DCRTPoly it stands for (utils/serial.h:99-103, dcrtpoly.h:349-354).  Blocking. */
   std::string Serialize() const {
+    single("Serialize");
     std::string blob(fhe_serial_bytes(ring_->handle()) * batch_, '\0');
     PimManager::check(fhe_serialize(ring_->handle(), &blob[0], d_, batch_, (int)format_, stream_), "Serialize");
     PimManager::check(fhe_sync(ctx(), stream_), "Serialize");
@@ -216,6 +259,7 @@ public:
    * when a stream is malformed or was written for another ring.  *consumed = bytes read. */
   static PimDCRTPoly Deserialize(std::shared_ptr<PimRing> ring, const void *blob, size_t len, size_t batch,
                                  size_t *consumed = nullptr, int stream = 0) {
+    if (ring->devices() > 1) throw pim_not_implemented_error("Deserialize needs a single-device PimManager");
     PimDCRTPoly p(std::move(ring), batch, PIM_EVALUATION, nullptr, stream);
     int fmt = 0;
     PimManager::check(fhe_deserialize(p.ring_->handle(), p.d_, blob, len, batch, &fmt, consumed, stream), "Deserialize");
@@ -235,16 +279,15 @@ public:
   PimDCRTPoly &operator*=(const PimDCRTPoly &rhs) { return inplace(rhs, FHE_OP_MUL); }
 
   void SwitchFormat() {
-    if (format_ == PIM_COEFFICIENT) {
-      PimManager::check(fhe_ntt_forward(ring_->handle(), d_, batch_, stream_), "SwitchFormat");
-      format_ = PIM_EVALUATION;
-    } else {
-      PimManager::check(fhe_ntt_inverse(ring_->handle(), d_, batch_, stream_), "SwitchFormat");
-      format_ = PIM_COEFFICIENT;
-    }
+    const int inverse = format_ == PIM_COEFFICIENT ? 0 : 1;
+    if (multi()) PimManager::check(fhe_group_ntt(ring_->group_handle(), dv_.data(), batch_, inverse, stream_), "SwitchFormat");
+    else if (inverse) PimManager::check(fhe_ntt_inverse(ring_->handle(), d_, batch_, stream_), "SwitchFormat");
+    else PimManager::check(fhe_ntt_forward(ring_->handle(), d_, batch_, stream_), "SwitchFormat");
+    format_ = inverse ? PIM_COEFFICIENT : PIM_EVALUATION;
   }
   /* dcrtpoly-impl.h:348-358 -> poly-impl.h:312-365; k even throws math_error there */
   PimDCRTPoly AutomorphismTransform(uint32_t k) const {
+    single("AutomorphismTransform");
     if (k % 2 == 0) throw pim_math_error("Automorphism index not odd\n");
     PimDCRTPoly out(ring_, batch_, format_, nullptr, stream_);
     PimManager::check(fhe_automorphism(ring_->handle(), out.d_, d_, batch_, k, (int)format_, stream_), "AutomorphismTransform");
@@ -252,6 +295,7 @@ public:
   }
   /* dcrtpoly-impl.h:360-369 -> poly-impl.h:368-380; `precomp` = device copy of PrecomputeAutoMap's table */
   PimDCRTPoly AutomorphismTransform(uint32_t k, fhe_dptr precomp) const {
+    single("AutomorphismTransform");
     if (format_ != PIM_EVALUATION)
       throw pim_not_implemented_error("Automorphism Poly Format not EVALUATION or not power-of-two");
     if (k % 2 == 0) throw pim_math_error("Automorphism index not odd\n");
@@ -263,6 +307,8 @@ public:
 
   /* dcrtpoly-impl.h:1034-1082: this over basis.From() -> result over basis.To(), same format flag */
   PimDCRTPoly ApproxSwitchCRTBasis(const PimBasis &basis) const {
+    single("SwitchCRTBasis");
+    single("ApproxSwitchCRTBasis");
     PimDCRTPoly out(basis.To(), batch_, format_, nullptr, stream_);
     PimManager::check(fhe_approx_switch_crt_basis(basis.handle(), out.d_, d_, batch_, stream_), "ApproxSwitchCRTBasis");
     return out;
@@ -270,12 +316,14 @@ public:
   /* dcrtpoly-impl.h:1085-1133 (the reference works in place; here the extended polynomial is returned): this over Q,
    * qToP from Q to P, ringQP the ring of Q followed by P.  Result in EVALUATION. */
   PimDCRTPoly ApproxModUp(const PimBasis &qToP, const std::shared_ptr<PimRing> &ringQP) const {
+    single("ApproxModUp");
     PimDCRTPoly out(ringQP, batch_, PIM_EVALUATION, nullptr, stream_);
     PimManager::check(fhe_approx_mod_up(qToP.handle(), out.d_, d_, batch_, (int)format_, stream_), "ApproxModUp");
     return out;
   }
   /* dcrtpoly-impl.h:1136-1175: this over QP in EVALUATION, pToQ from P to Q; t > 0 selects the BGV form */
   PimDCRTPoly ApproxModDown(const PimBasis &pToQ, uint64_t t = 0) const {
+    single("ApproxModDown");
     if (format_ != PIM_EVALUATION) throw pim_not_implemented_error("ApproxModDown expects Format::EVALUATION");
     PimDCRTPoly out(pToQ.To(), batch_, PIM_EVALUATION, nullptr, stream_);
     PimManager::check(fhe_approx_mod_down(pToQ.handle(), out.d_, d_, batch_, t, stream_), "ApproxModDown");
@@ -289,6 +337,7 @@ public:
   }
   /* dcrtpoly-impl.h:1311-1358 (in place in the reference) */
   PimDCRTPoly ExpandCRTBasis(const PimBasis &qToP, const std::shared_ptr<PimRing> &ringQP, PimFormat resultFormat) const {
+    single("ExpandCRTBasis");
     PimDCRTPoly out(ringQP, batch_, resultFormat, nullptr, stream_);
     PimManager::check(fhe_expand_crt_basis(qToP.handle(), out.d_, d_, batch_, (int)format_, (int)resultFormat, stream_),
                       "ExpandCRTBasis");
@@ -297,6 +346,7 @@ public:
   /* dcrtpoly-impl.h:1361-1410 (in place in the reference): ringPQ holds the P towers first */
   PimDCRTPoly ExpandCRTBasisReverseOrder(const PimBasis &qToP, const std::shared_ptr<PimRing> &ringPQ,
                                          PimFormat resultFormat) const {
+    single("ExpandCRTBasisReverseOrder");
     PimDCRTPoly out(ringPQ, batch_, resultFormat, nullptr, stream_);
     PimManager::check(fhe_expand_crt_basis_reverse_order(qToP.handle(), out.d_, d_, batch_, (int)format_, (int)resultFormat,
                                                          stream_), "ExpandCRTBasisReverseOrder");
@@ -306,6 +356,7 @@ public:
    * switch back; ringQlPl = [Ql | Pl] */
   PimDCRTPoly FastExpandCRTBasisPloverQ(const PimBasis &qToPl, const PimBasis &plToQl,
                                         const std::shared_ptr<PimRing> &ringQlPl) const {
+    single("FastExpandCRTBasisPloverQ");
     PimDCRTPoly out(ringQlPl, batch_, format_, nullptr, stream_);
     PimManager::check(fhe_fast_expand_crt_basis_pl_over_q(qToPl.handle(), plToQl.handle(), out.d_, d_, batch_, stream_),
                       "FastExpandCRTBasisPloverQ");
@@ -313,6 +364,7 @@ public:
   }
   /* dcrtpoly-impl.h:1514-1534 (in place in the reference): this over the first towers of plan.Ring() */
   PimDCRTPoly ExpandCRTBasisQlHat(const PimTowerScale &plan) const {
+    single("ExpandCRTBasisQlHat");
     PimDCRTPoly out(plan.Ring(), batch_, format_, nullptr, stream_);
     PimManager::check(fhe_expand_crt_basis_ql_hat(plan.handle(), (uint32_t)ring_->GetNumTowers(), out.d_, d_, batch_, stream_),
                       "ExpandCRTBasisQlHat");
@@ -320,6 +372,7 @@ public:
   }
   /* dcrtpoly-impl.h:617-627: Times(const std::vector<NativeInteger>&), one constant per tower */
   PimDCRTPoly Times(const PimTowerScale &plan) const {
+    single("Times");
     if (ring_->GetNumTowers() != plan.Ring()->GetNumTowers()) throw pim_math_error("tower size mismatch; cannot multiply");
     PimDCRTPoly out(ring_, batch_, format_, nullptr, stream_);
     PimManager::check(fhe_dcrt_times_towers(plan.handle(), out.d_, d_, batch_, stream_), "Times");
@@ -327,6 +380,7 @@ public:
   }
   /* dcrtpoly-impl.h:2052-2066 (in place in the reference): this over plan.Ring() plus one tower */
   PimDCRTPoly ScaleAndRoundPOverQ(const PimTowerScale &plan) const {
+    single("ScaleAndRoundPOverQ");
     if (ring_->GetNumTowers() != plan.Ring()->GetNumTowers() + 1)
       throw pim_math_error("ScaleAndRoundPOverQ: the input must have one tower more than the output basis");
     PimDCRTPoly out(plan.Ring(), batch_, format_, nullptr, stream_);
@@ -335,6 +389,7 @@ public:
   }
   /* dcrtpoly-impl.h:1876-1960 */
   PimDCRTPoly ScaleAndRound(const PimScaleRound &plan) const {
+    single("ScaleAndRound");
     PimDCRTPoly out(plan.Out(), batch_, format_, nullptr, stream_);
     PimManager::check(fhe_scale_and_round(plan.handle(), out.d_, d_, batch_, stream_), "ScaleAndRound");
     return out;
@@ -342,6 +397,7 @@ public:
   /* dcrtpoly-impl.h:746-769 (in place in the reference).  As there, a COEFFICIENT input comes back with forward-
    * transformed towers while the format flag stays COEFFICIENT (dcrtpoly-impl.h:765-766). */
   PimDCRTPoly DropLastElementAndScale(const PimRescale &plan) const {
+    single("DropLastElementAndScale");
     PimDCRTPoly out(plan.Rest(), batch_, format_, nullptr, stream_);
     PimManager::check(fhe_drop_last_element_and_scale(plan.handle(), out.d_, d_, batch_, (int)format_, stream_),
                       "DropLastElementAndScale");
@@ -349,13 +405,39 @@ public:
   }
   /* dcrtpoly-impl.h:792-812 */
   PimDCRTPoly ModReduce(const PimRescale &plan, uint64_t t) const {
+    single("ModReduce");
     PimDCRTPoly out(plan.Rest(), batch_, format_, nullptr, stream_);
     PimManager::check(fhe_mod_reduce(plan.handle(), out.d_, d_, batch_, t, (int)format_, stream_), "ModReduce");
     return out;
   }
 
 private:
-  fhe_ctx *ctx() const { return ring_->manager()->context(); }
+  fhe_ctx *ctx(uint32_t rank = 0) const { return ring_->manager()->context(rank); }
+  bool multi() const { return !dv_.empty(); }
+  fhe_dptr ptr(uint32_t rank) const { return multi() ? dv_[rank] : d_; }
+  size_t block_bytes(uint32_t rank) const {
+    if (!multi()) return bytes();
+    size_t first, count;
+    GetBlock(rank, &first, &count);
+    return count * ring_->GetNumTowers() * ring_->GetRingDimension() * sizeof(uint64_t);
+  }
+  void allocate() {
+    if (ring_->devices() > 1) {
+      if (!ring_->group_handle()) throw pim_not_implemented_error("PimDCRTPoly over a ring view needs a single-device PimManager");
+      dv_.assign(ring_->devices(), 0);
+      PimManager::check(fhe_group_alloc(ring_->group_handle(), batch_, dv_.data()), "PimDCRTPoly");
+      d_ = dv_[0];
+    } else {
+      PimManager::check(fhe_alloc(ctx(), bytes() ? bytes() : 8, &d_), "PimDCRTPoly");
+    }
+  }
+  void sync_streams(const char *what) const {
+    for (uint32_t i = 0; i < devices(); i++) PimManager::check(fhe_sync(ctx(i), stream_), what);
+  }
+  void single(const char *what) const {
+    if (multi()) throw pim_not_implemented_error(std::string(what) + " needs a single-device PimManager (the batch is split over " +
+                                                 std::to_string(devices()) + " devices)");
+  }
 
   void check(const PimDCRTPoly &rhs, const char *verb, bool need_eval) const {
     if (ring_->GetRingDimension() != rhs.ring_->GetRingDimension()) throw pim_math_error("RingDimension missmatch");
@@ -372,19 +454,27 @@ private:
   }
   PimDCRTPoly binary(const PimDCRTPoly &rhs, int op) const {
     PimDCRTPoly out(ring_, batch_, format_, nullptr, stream_);
-    PimManager::check(fhe_dcrt_op(ring_->handle(), op, out.d_, d_, rhs.d_, batch_, stream_), "DCRTPoly op");
+    run_op(op, out, rhs);
     return out;
   }
   PimDCRTPoly &inplace(const PimDCRTPoly &rhs, int op) {
-    PimManager::check(fhe_dcrt_op(ring_->handle(), op, d_, d_, rhs.d_, batch_, stream_), "DCRTPoly op");
+    run_op(op, *this, rhs);
     return *this;
+  }
+  void run_op(int op, const PimDCRTPoly &dst, const PimDCRTPoly &rhs) const {
+    if (multi())
+      PimManager::check(fhe_group_dcrt_op(ring_->group_handle(), op, dst.dv_.data(), dv_.data(), rhs.dv_.data(), batch_, stream_),
+                        "DCRTPoly op");
+    else
+      PimManager::check(fhe_dcrt_op(ring_->handle(), op, dst.d_, d_, rhs.d_, batch_, stream_), "DCRTPoly op");
   }
 
   std::shared_ptr<PimRing> ring_;
   size_t batch_;
   PimFormat format_;
   int stream_;
-  fhe_dptr d_ = 0;
+  fhe_dptr d_ = 0;                 /* single device: the batch; several: the first device's block (= dv_[0]) */
+  std::vector<fhe_dptr> dv_;       /* several devices: one block per device */
 };
 
 #endif /* _PIM_DCRT_POLY_ */

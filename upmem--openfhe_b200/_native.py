@@ -94,6 +94,28 @@ SIGNATURES = {
     "fhe_dcrt_chain_host": (ci, [vp, ctypes.POINTER(ci), ci, vp, vp, sz]),
     "fhe_ntt_host": (ci, [vp, vp, sz, ci]),
     "fhe_imad_probe": (ci, [vp, ci, ci, ci, ctypes.POINTER(ctypes.c_float)]),
+    "fhe_group_create": (ci, [ci, vp, ctypes.c_char_p, ctypes.POINTER(vp)]),
+    "fhe_group_destroy": (ci, [vp]),
+    "fhe_group_size": (ci, [vp]),
+    "fhe_group_ctx": (vp, [vp, ci]),
+    "fhe_group_sync": (ci, [vp]),
+    "fhe_group_partition": (ci, [vp, sz, ci, ctypes.POINTER(sz), ctypes.POINTER(sz)]),
+    "fhe_group_launch": (ci, [vp, ci, vp, pu64]),
+    "fhe_group_ring_create": (ci, [vp, u32, u32, vp, vp, ctypes.POINTER(vp)]),
+    "fhe_group_ring_destroy": (ci, [vp]),
+    "fhe_group_ring_at": (vp, [vp, ci]),
+    "fhe_group_alloc": (ci, [vp, sz, pu64]),
+    "fhe_group_free": (ci, [vp, pu64]),
+    "fhe_group_scatter": (ci, [vp, pu64, vp, sz, ci]),
+    "fhe_group_gather": (ci, [vp, vp, pu64, sz, ci]),
+    "fhe_group_dcrt_op": (ci, [vp, ci, pu64, pu64, pu64, sz, ci]),
+    "fhe_group_ntt": (ci, [vp, pu64, sz, ci, ci]),
+    "fhe_group_all_gather": (ci, [vp, pu64, pu64, sz, ci]),
+    "fhe_group_chain_host": (ci, [vp, ctypes.POINTER(ci), ci, vp, vp, sz]),
+    "fhe_comm_unique_id": (ci, [vp, sz]),
+    "fhe_comm_create": (ci, [vp, ci, ci, vp, ctypes.POINTER(vp)]),
+    "fhe_comm_destroy": (ci, [vp]),
+    "fhe_comm_all_gather": (ci, [vp, u64, u64, sz, ci]),
 }
 
 FHE_OK, FHE_EINVAL, FHE_ECUDA, FHE_ENOMEM, FHE_ENODEV, FHE_EUNSUPPORTED = 0, -1, -2, -3, -4, -5

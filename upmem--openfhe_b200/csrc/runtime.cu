@@ -1783,3 +1783,388 @@ extern "C" int fhe_imad_probe(fhe_ctx* ctx, int blocks, int threads, int iters, 
     arena_park(ctx, out);
     return rc;
 }
+
+// ---------------------------------------------------------------------------------------------
+// several devices of one node: the batch is split in contiguous blocks, one per device, every
+// device holds the ring's tables, no collective runs inside the path.  NCCL (loaded at run time: libnccl.so.2)
+// carries only the optional gather of results over NVLink / NVSwitch, on the library's own streams.
+// Replaces the scatter of PimManager::copy_to_pim over `nr_dpus` DPUs (src/core/pim/host/PimManager.cpp:15-24).
+// ---------------------------------------------------------------------------------------------
+#include <dlfcn.h>
+#include <nccl.h>
+
+namespace {
+struct NcclApi {
+    void* h = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    std::string why;
+};
+
+NcclApi* nccl_api() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        for (const char* name : {"libnccl.so.2", "libnccl.so"}) {
+            api.h = dlopen(name, RTLD_NOW | RTLD_LOCAL);
+            if (api.h) break;
+        }
+        if (!api.h) { api.why = dlerror() ? dlerror() : "libnccl.so.2 not found"; return; }
+        auto sym = [&](const char* n) { void* p = dlsym(api.h, n); if (!p) api.why = std::string("missing symbol ") + n; return p; };
+        api.GetUniqueId = (decltype(api.GetUniqueId))sym("ncclGetUniqueId");
+        api.CommInitRank = (decltype(api.CommInitRank))sym("ncclCommInitRank");
+        api.CommInitAll = (decltype(api.CommInitAll))sym("ncclCommInitAll");
+        api.CommDestroy = (decltype(api.CommDestroy))sym("ncclCommDestroy");
+        api.GroupStart = (decltype(api.GroupStart))sym("ncclGroupStart");
+        api.GroupEnd = (decltype(api.GroupEnd))sym("ncclGroupEnd");
+        api.AllGather = (decltype(api.AllGather))sym("ncclAllGather");
+        api.Send = (decltype(api.Send))sym("ncclSend");
+        api.Recv = (decltype(api.Recv))sym("ncclRecv");
+        api.GetErrorString = (decltype(api.GetErrorString))sym("ncclGetErrorString");
+        if (!api.why.empty()) { dlclose(api.h); api.h = nullptr; }
+    });
+    return api.h ? &api : nullptr;
+}
+#define NCCL_TRY(api, expr)                                                                              \
+    do {                                                                                                 \
+        ncclResult_t r__ = (expr);                                                                       \
+        if (r__ != ncclSuccess) return fail(FHE_ECUDA, "%s failed: %s", #expr, (api)->GetErrorString(r__)); \
+    } while (0)
+
+void partition(size_t batch, int n, int rank, size_t* first, size_t* count) {
+    size_t base = batch / n, rem = batch % n;
+    *count = base + ((size_t)rank < rem ? 1 : 0);
+    *first = (size_t)rank * base + std::min<size_t>(rank, rem);
+}
+}  // namespace
+
+struct fhe_comm {
+    fhe_ctx* ctx = nullptr;
+    ncclComm_t comm = nullptr;
+    int nranks = 0, rank = 0;
+};
+
+extern "C" int fhe_comm_unique_id(void* id, size_t cap) {
+    NcclApi* api = nccl_api();
+    if (!api) return fail(FHE_EUNSUPPORTED, "NCCL is not available: %s", nccl_api() ? "" : "libnccl.so.2 could not be loaded");
+    if (!id || cap < sizeof(ncclUniqueId)) return fail(FHE_EINVAL, "fhe_comm_unique_id: need a buffer of %zu bytes", sizeof(ncclUniqueId));
+    ncclUniqueId u;
+    NCCL_TRY(api, api->GetUniqueId(&u));
+    memcpy(id, &u, sizeof(u));
+    return FHE_OK;
+}
+
+extern "C" int fhe_comm_create(fhe_ctx* ctx, int nranks, int rank, const void* id, fhe_comm** out) {
+    if (!ctx || !id || !out) return fail(FHE_EINVAL, "fhe_comm_create: null argument");
+    *out = nullptr;
+    if (nranks < 1 || rank < 0 || rank >= nranks) return fail(FHE_EINVAL, "fhe_comm_create: rank %d not in [0,%d)", rank, nranks);
+    NcclApi* api = nccl_api();
+    if (!api) return fail(FHE_EUNSUPPORTED, "NCCL is not available (libnccl.so.2 could not be loaded)");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    ncclUniqueId u;
+    memcpy(&u, id, sizeof(u));
+    auto* c = new fhe_comm;
+    c->ctx = ctx; c->nranks = nranks; c->rank = rank;
+    ncclResult_t r = api->CommInitRank(&c->comm, nranks, u, rank);
+    if (r != ncclSuccess) { delete c; return fail(FHE_ECUDA, "ncclCommInitRank failed: %s", api->GetErrorString(r)); }
+    *out = c;
+    return FHE_OK;
+}
+
+extern "C" int fhe_comm_destroy(fhe_comm* c) {
+    if (!c) return FHE_OK;
+    NcclApi* api = nccl_api();
+    if (api && c->comm) { cudaSetDevice(c->ctx->device); api->CommDestroy(c->comm); }
+    delete c;
+    return FHE_OK;
+}
+
+extern "C" int fhe_comm_all_gather(fhe_comm* c, fhe_dptr dst, fhe_dptr src, size_t words, int stream) {
+    if (!c) return fail(FHE_EINVAL, "null communicator");
+    StreamRef s;
+    int rc = get_stream(c->ctx, stream, &s);
+    if (rc) return rc;
+    if (words == 0) return FHE_OK;
+    if (!dst || !src) return fail(FHE_EINVAL, "fhe_comm_all_gather: null device pointer");
+    NcclApi* api = nccl_api();
+    CUDA_TRY(cudaSetDevice(c->ctx->device));
+    NCCL_TRY(api, api->AllGather((const void*)(uintptr_t)src, (void*)(uintptr_t)dst, words, ncclUint64, c->comm, s));
+    return FHE_OK;
+}
+
+struct fhe_group {
+    std::vector<fhe_ctx*> ctx;
+    std::vector<ncclComm_t> comms;       // created on first use (fhe_group_all_gather)
+    std::mutex mu;
+};
+struct fhe_group_ring {
+    fhe_group* g = nullptr;
+    std::vector<fhe_ring*> rings;
+};
+
+extern "C" int fhe_group_destroy(fhe_group* g) {
+    if (!g) return FHE_OK;
+    NcclApi* api = nccl_api();
+    for (size_t i = 0; i < g->comms.size(); i++)
+        if (api && g->comms[i]) { cudaSetDevice(g->ctx[i]->device); api->CommDestroy(g->comms[i]); }
+    for (fhe_ctx* c : g->ctx) fhe_shutdown(c);
+    delete g;
+    return FHE_OK;
+}
+
+extern "C" int fhe_group_create(int ndev, const int* devices, const char* opts, fhe_group** out) {
+    if (!out) return fail(FHE_EINVAL, "fhe_group_create: out is null");
+    *out = nullptr;
+    int have = 0;
+    cudaError_t e = cudaGetDeviceCount(&have);
+    if (e != cudaSuccess || have == 0) {
+        cudaGetLastError();
+        return fail(FHE_ENODEV, "fhe_group_create: no CUDA device (%s); this backend has no CPU fallback",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    }
+    if (ndev <= 0) ndev = have;                       // 0: every visible device
+    if (ndev > have && !devices) return fail(FHE_EINVAL, "fhe_group_create: %d devices requested, %d visible", ndev, have);
+    auto* g = new fhe_group;
+    for (int i = 0; i < ndev; i++) {
+        int dev = devices ? devices[i] : i;
+        for (fhe_ctx* c : g->ctx)
+            if (c->device == dev) { fhe_group_destroy(g); return fail(FHE_EINVAL, "fhe_group_create: device %d listed twice", dev); }
+        fhe_ctx* c = nullptr;
+        int rc = fhe_init(dev, opts, &c);
+        if (rc) { fhe_group_destroy(g); return rc; }
+        g->ctx.push_back(c);
+    }
+    *out = g;
+    return FHE_OK;
+}
+
+extern "C" int fhe_group_size(const fhe_group* g) { return g ? (int)g->ctx.size() : 0; }
+extern "C" fhe_ctx* fhe_group_ctx(fhe_group* g, int rank) {
+    return (g && rank >= 0 && rank < (int)g->ctx.size()) ? g->ctx[rank] : nullptr;
+}
+
+extern "C" int fhe_group_sync(fhe_group* g) {
+    if (!g) return fail(FHE_EINVAL, "null group");
+    for (fhe_ctx* c : g->ctx) {
+        int rc = fhe_sync(c, -2);
+        if (rc) return rc;
+    }
+    return FHE_OK;
+}
+
+extern "C" int fhe_group_partition(const fhe_group* g, size_t batch, int rank, size_t* first, size_t* count) {
+    if (!g || !first || !count) return fail(FHE_EINVAL, "fhe_group_partition: null argument");
+    if (rank < 0 || rank >= (int)g->ctx.size()) return fail(FHE_EINVAL, "fhe_group_partition: rank %d not in [0,%zu)", rank, g->ctx.size());
+    partition(batch, (int)g->ctx.size(), rank, first, count);
+    return FHE_OK;
+}
+
+// Legacy descriptor on every device at once: the descriptor's sizes are per device (PimData divides them by
+// getNumDpus(), pim/PimData.h:281-290), heap_bases[rank] is that device's heap.  Blocking, like start_kernel().
+extern "C" int fhe_group_launch(fhe_group* g, int kernel_id, const void* desc, const fhe_dptr* heap_bases) {
+    if (!g || !desc || !heap_bases) return fail(FHE_EINVAL, "fhe_group_launch: null argument");
+    const size_t n = g->ctx.size();
+    if (n == 1) return fhe_launch(g->ctx[0], kernel_id, desc, heap_bases[0]);
+    std::vector<int> rcs(n, FHE_OK);
+    std::vector<std::string> msgs(n);
+    std::vector<std::thread> th;
+    for (size_t i = 0; i < n; i++)
+        th.emplace_back([&, i] {
+            rcs[i] = fhe_launch(g->ctx[i], kernel_id, desc, heap_bases[i]);
+            if (rcs[i]) msgs[i] = fhe_last_error();
+        });
+    for (auto& t : th) t.join();
+    for (size_t i = 0; i < n; i++)
+        if (rcs[i]) return fail(rcs[i], "device %d: %s", g->ctx[i]->device, msgs[i].c_str());
+    return FHE_OK;
+}
+
+extern "C" int fhe_group_ring_destroy(fhe_group_ring* r) {
+    if (!r) return FHE_OK;
+    for (fhe_ring* x : r->rings) fhe_ring_destroy(x);
+    delete r;
+    return FHE_OK;
+}
+
+extern "C" int fhe_group_ring_create(fhe_group* g, uint32_t N, uint32_t towers, const uint64_t* q, const uint64_t* psi,
+                                     fhe_group_ring** out) {
+    if (!g || !out) return fail(FHE_EINVAL, "fhe_group_ring_create: null argument");
+    *out = nullptr;
+    auto* r = new fhe_group_ring;
+    r->g = g;
+    for (fhe_ctx* c : g->ctx) {
+        fhe_ring* x = nullptr;
+        int rc = fhe_ring_create(c, N, towers, q, psi, &x);
+        if (rc) { fhe_group_ring_destroy(r); return rc; }
+        r->rings.push_back(x);
+    }
+    *out = r;
+    return FHE_OK;
+}
+
+extern "C" fhe_ring* fhe_group_ring_at(fhe_group_ring* r, int rank) {
+    return (r && rank >= 0 && rank < (int)r->rings.size()) ? r->rings[rank] : nullptr;
+}
+
+// per-device work on each device's block of the batch; launches are asynchronous, so the devices run concurrently
+template <class F>
+static int group_each(fhe_group_ring* r, size_t batch, F f) {
+    if (!r) return fail(FHE_EINVAL, "null group ring");
+    const int n = (int)r->rings.size();
+    for (int i = 0; i < n; i++) {
+        size_t first, count;
+        partition(batch, n, i, &first, &count);
+        if (count == 0) continue;
+        int rc = f(i, r->rings[i], first, count);
+        if (rc) return rc;
+    }
+    return FHE_OK;
+}
+
+extern "C" int fhe_group_dcrt_op(fhe_group_ring* r, int op, const fhe_dptr* dst, const fhe_dptr* a, const fhe_dptr* b,
+                                 size_t batch, int stream) {
+    if (!dst || !a || !b) return fail(FHE_EINVAL, "fhe_group_dcrt_op: null argument");
+    return group_each(r, batch, [&](int i, fhe_ring* x, size_t, size_t count) { return fhe_dcrt_op(x, op, dst[i], a[i], b[i], count, stream); });
+}
+
+extern "C" int fhe_group_ntt(fhe_group_ring* r, const fhe_dptr* x, size_t batch, int inverse, int stream) {
+    if (!x) return fail(FHE_EINVAL, "fhe_group_ntt: null argument");
+    return group_each(r, batch, [&](int i, fhe_ring* ring, size_t, size_t count) { return fhe_ntt_algo(ring, x[i], count, inverse, 0, stream); });
+}
+
+extern "C" int fhe_group_alloc(fhe_group_ring* r, size_t batch, fhe_dptr* out) {
+    if (!r || !out) return fail(FHE_EINVAL, "fhe_group_alloc: null argument");
+    const int n = (int)r->rings.size();
+    for (int i = 0; i < n; i++) out[i] = 0;
+    for (int i = 0; i < n; i++) {
+        size_t first, count;
+        partition(batch, n, i, &first, &count);
+        int rc = fhe_alloc(r->g->ctx[i], std::max<size_t>(count, 1) * r->rings[i]->dev.T * r->rings[i]->dev.N * 8, &out[i]);
+        if (rc) {
+            for (int k = 0; k < i; k++) { fhe_free(r->g->ctx[k], out[k]); out[k] = 0; }
+            return rc;
+        }
+    }
+    return FHE_OK;
+}
+
+extern "C" int fhe_group_free(fhe_group_ring* r, const fhe_dptr* p) {
+    if (!r || !p) return fail(FHE_EINVAL, "fhe_group_free: null argument");
+    int first_rc = FHE_OK;
+    for (size_t i = 0; i < r->rings.size(); i++) {
+        int rc = fhe_free(r->g->ctx[i], p[i]);
+        if (rc && !first_rc) first_rc = rc;
+    }
+    return first_rc;
+}
+
+// host [batch][T][N] -> each device's block, and back.  Asynchronous on `stream` of every device when the host
+// buffer is pinned; fhe_group_sync (or a later blocking call) completes them.
+extern "C" int fhe_group_scatter(fhe_group_ring* r, const fhe_dptr* dst, const uint64_t* host, size_t batch, int stream) {
+    if (!dst || (batch && !host)) return fail(FHE_EINVAL, "fhe_group_scatter: null argument");
+    return group_each(r, batch, [&](int i, fhe_ring* x, size_t first, size_t count) {
+        size_t item = (size_t)x->dev.T * x->dev.N;
+        return fhe_h2d(r->g->ctx[i], dst[i], host + first * item, count * item * 8, stream);
+    });
+}
+extern "C" int fhe_group_gather(fhe_group_ring* r, uint64_t* host, const fhe_dptr* src, size_t batch, int stream) {
+    if (!src || (batch && !host)) return fail(FHE_EINVAL, "fhe_group_gather: null argument");
+    return group_each(r, batch, [&](int i, fhe_ring* x, size_t first, size_t count) {
+        size_t item = (size_t)x->dev.T * x->dev.N;
+        return fhe_d2h(r->g->ctx[i], host + first * item, src[i], count * item * 8, stream);
+    });
+}
+
+// Every device receives every block: dst[rank] = the whole [batch][T][N] result, HBM to HBM over NVLink / NVSwitch
+// (north_star: "NCCL over NVLink only to gather results").  ncclAllGather when the blocks are equal, grouped
+// ncclSend / ncclRecv otherwise.  Enqueued on `stream` of every device; complete after fhe_group_sync.
+extern "C" int fhe_group_all_gather(fhe_group_ring* r, const fhe_dptr* dst, const fhe_dptr* src, size_t batch, int stream) {
+    if (!r || !dst || !src) return fail(FHE_EINVAL, "fhe_group_all_gather: null argument");
+    fhe_group* g = r->g;
+    const int n = (int)g->ctx.size();
+    if (batch == 0) return FHE_OK;
+    const size_t item = (size_t)r->rings[0]->dev.T * r->rings[0]->dev.N;
+    if (n == 1) return fhe_d2d(g->ctx[0], dst[0], src[0], batch * item * 8, stream);
+    NcclApi* api = nccl_api();
+    if (!api) return fail(FHE_EUNSUPPORTED, "NCCL is not available (libnccl.so.2 could not be loaded)");
+    {
+        std::lock_guard<std::mutex> lk(g->mu);
+        if (g->comms.empty()) {
+            std::vector<int> devs;
+            for (fhe_ctx* c : g->ctx) devs.push_back(c->device);
+            g->comms.assign(n, nullptr);
+            ncclResult_t rr = api->CommInitAll(g->comms.data(), n, devs.data());
+            if (rr != ncclSuccess) { g->comms.clear(); return fail(FHE_ECUDA, "ncclCommInitAll failed: %s", api->GetErrorString(rr)); }
+        }
+    }
+    std::vector<cudaStream_t> st(n);
+    for (int i = 0; i < n; i++) {
+        if (stream == FHE_STREAM_LEGACY) st[i] = cudaStreamLegacy;
+        else if (stream < 0 || stream >= (int)g->ctx[i]->streams.size()) return fail(FHE_EINVAL, "fhe_group_all_gather: bad stream index %d", stream);
+        else st[i] = g->ctx[i]->streams[stream];
+    }
+    const bool even = batch % n == 0;
+    NCCL_TRY(api, api->GroupStart());
+    for (int i = 0; i < n; i++) {
+        cudaSetDevice(g->ctx[i]->device);
+        if (even) {
+            ncclResult_t rr = api->AllGather((const void*)(uintptr_t)src[i], (void*)(uintptr_t)dst[i], batch / n * item, ncclUint64, g->comms[i], st[i]);
+            if (rr != ncclSuccess) { api->GroupEnd(); return fail(FHE_ECUDA, "ncclAllGather failed: %s", api->GetErrorString(rr)); }
+            continue;
+        }
+        size_t myfirst, mycount;
+        partition(batch, n, i, &myfirst, &mycount);
+        for (int p = 0; p < n; p++) {
+            size_t pfirst, pcount;
+            partition(batch, n, p, &pfirst, &pcount);
+            ncclResult_t rr = ncclSuccess;
+            if (p == i) {
+                if (mycount && cudaMemcpyAsync((void*)(uintptr_t)(dst[i] + myfirst * item * 8), (const void*)(uintptr_t)src[i], mycount * item * 8,
+                                               cudaMemcpyDeviceToDevice, st[i]) != cudaSuccess) rr = ncclUnhandledCudaError;
+            } else {
+                if (mycount) rr = api->Send((const void*)(uintptr_t)src[i], mycount * item, ncclUint64, p, g->comms[i], st[i]);
+                if (rr == ncclSuccess && pcount)
+                    rr = api->Recv((void*)(uintptr_t)(dst[i] + pfirst * item * 8), pcount * item, ncclUint64, p, g->comms[i], st[i]);
+            }
+            if (rr != ncclSuccess) { api->GroupEnd(); return fail(FHE_ECUDA, "NCCL send/recv failed: %s", api->GetErrorString(rr)); }
+        }
+    }
+    NCCL_TRY(api, api->GroupEnd());
+    for (int i = 0; i < n; i++) {
+        int slot = stream == FHE_STREAM_LEGACY ? (int)g->ctx[i]->streams.size() : stream;
+        g->ctx[i]->epoch[slot].fetch_add(1, std::memory_order_release);
+    }
+    return FHE_OK;
+}
+
+// The in-place operator sequence on HOST operands over all devices: each device streams its block of the batch through
+// its own pipeline (fhe_dcrt_chain_host), one host thread per device.  Blocking.
+extern "C" int fhe_group_chain_host(fhe_group_ring* r, const int* ops, int nops, uint64_t* a, const uint64_t* b, size_t batch) {
+    if (!r) return fail(FHE_EINVAL, "null group ring");
+    const int n = (int)r->rings.size();
+    if (n == 1) return fhe_dcrt_chain_host(r->rings[0], ops, nops, a, b, batch);
+    std::vector<int> rcs(n, FHE_OK);
+    std::vector<std::string> msgs(n);
+    std::vector<std::thread> th;
+    for (int i = 0; i < n; i++)
+        th.emplace_back([&, i] {
+            size_t first, count;
+            partition(batch, n, i, &first, &count);
+            if (!count) return;
+            size_t item = (size_t)r->rings[i]->dev.T * r->rings[i]->dev.N;
+            rcs[i] = fhe_dcrt_chain_host(r->rings[i], ops, nops, a + first * item, b ? b + first * item : nullptr, count);
+            if (rcs[i]) msgs[i] = fhe_last_error();
+        });
+    for (auto& t : th) t.join();
+    for (int i = 0; i < n; i++)
+        if (rcs[i]) return fail(rcs[i], "device %d: %s", r->g->ctx[i]->device, msgs[i].c_str());
+    return FHE_OK;
+}

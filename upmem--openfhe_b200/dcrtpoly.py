@@ -600,3 +600,133 @@ def hps_scale_tables(q, r, t):
             modr[j, i] = ((t * R * pow(QR // qi, -1, qi)) // qi) % rj
         modr[j, len(q)] = ((t * R * pow(QR // rj, -1, rj)) // rj) % rj
     return frac, modr
+
+
+class Group:
+    """Several B200s of one node driven by this process (fhe_group_*): what PimManager::getPim(nr_dpus) hands out when
+    `nr_dpus` devices are asked for (src/core/include/pim/PimManager.h:23-29).  The batch is split in contiguous
+    blocks, one per device; NCCL inside libfhe_b200.so carries only the optional gather."""
+
+    def __init__(self, ndev=0, devices=None, opts=""):
+        h = ctypes.c_void_p()
+        devs = None if devices is None else (ctypes.c_int * len(devices))(*devices)
+        N.check(N.lib.fhe_group_create(ndev, devs, opts.encode() if opts else None, ctypes.byref(h)))
+        self.h = h
+        self.size = N.lib.fhe_group_size(h)
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_group_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def backend(self, rank):
+        """A Backend view of one device of the group (not owning: do not close it)."""
+        be = Backend.__new__(Backend)
+        be.h = ctypes.c_void_p(N.lib.fhe_group_ctx(self.h, rank))
+        be.device = N.lib.fhe_device(be.h)
+        return be
+
+    def partition(self, batch, rank):
+        first, count = ctypes.c_size_t(), ctypes.c_size_t()
+        N.check(N.lib.fhe_group_partition(self.h, batch, rank, ctypes.byref(first), ctypes.byref(count)))
+        return first.value, count.value
+
+    def sync(self):
+        N.check(N.lib.fhe_group_sync(self.h))
+
+
+class GroupRing:
+    """The same ring on every device of a Group, and the hot path over a batch split across them."""
+
+    def __init__(self, group, n, q, psi=None):
+        self.group = group
+        self.n = int(n)
+        self.q = np.ascontiguousarray(q, dtype=np.uint64)
+        self.psi = None if psi is None else np.ascontiguousarray(psi, dtype=np.uint64)
+        self.towers = len(self.q)
+        h = ctypes.c_void_p()
+        N.check(N.lib.fhe_group_ring_create(group.h, self.n, self.towers, _ptr(self.q),
+                                            None if self.psi is None else _ptr(self.psi), ctypes.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_group_ring_destroy(self.h)
+            self.h = None
+
+    def _arr(self, ptrs):
+        return (ctypes.c_uint64 * self.group.size)(*ptrs)
+
+    def words(self, batch):
+        return batch * self.towers * self.n
+
+    def alloc(self, batch):
+        out = (ctypes.c_uint64 * self.group.size)()
+        N.check(N.lib.fhe_group_alloc(self.h, batch, out))
+        return list(out)
+
+    def free(self, bufs):
+        N.check(N.lib.fhe_group_free(self.h, self._arr(bufs)))
+
+    def fill_uniform(self, bufs, batch, seed, stream=0):
+        """Seeded synthetic residues in every block (block r uses seed + 7919 * first_r)."""
+        for r in range(self.group.size):
+            first, count = self.group.partition(batch, r)
+            if count:
+                ring = ctypes.c_void_p(N.lib.fhe_group_ring_at(self.h, r))
+                N.check(N.lib.fhe_fill_uniform(ring, bufs[r], count, seed + 7919 * first, stream))
+
+    def scatter(self, bufs, host, batch, stream=0):
+        host = np.ascontiguousarray(host, dtype=np.uint64)
+        N.check(N.lib.fhe_group_scatter(self.h, self._arr(bufs), _ptr(host), batch, stream))
+        self.group.sync()
+
+    def gather(self, bufs, batch, stream=0):
+        out = np.empty((batch, self.towers, self.n), np.uint64)
+        N.check(N.lib.fhe_group_gather(self.h, _ptr(out), self._arr(bufs), batch, stream))
+        self.group.sync()
+        return out
+
+    def op(self, op, dst, a, b, batch, stream=0):
+        N.check(N.lib.fhe_group_dcrt_op(self.h, op, self._arr(dst), self._arr(a), self._arr(b), batch, stream))
+
+    def ntt(self, x, batch, inverse=False, stream=0):
+        N.check(N.lib.fhe_group_ntt(self.h, self._arr(x), batch, 1 if inverse else 0, stream))
+
+    def all_gather(self, dst, src, batch, stream=0):
+        N.check(N.lib.fhe_group_all_gather(self.h, self._arr(dst), self._arr(src), batch, stream))
+
+    def chain_host(self, ops, a, b, batch):
+        n = len(ops)
+        N.check(N.lib.fhe_group_chain_host(self.h, (ctypes.c_int * n)(*ops), n, _ptr(a), None if b is None else _ptr(b), batch))
+
+
+class Comm:
+    """One rank of a NCCL communicator owned by libfhe_b200.so (one-process-per-GPU callers, e.g. under torchrun):
+    rank 0 creates the id with Comm.unique_id() and the caller hands it to the other ranks."""
+
+    @staticmethod
+    def unique_id():
+        buf = ctypes.create_string_buffer(128)
+        N.check(N.lib.fhe_comm_unique_id(buf, 128))
+        return buf.raw
+
+    def __init__(self, backend, nranks, rank, uid):
+        h = ctypes.c_void_p()
+        N.check(N.lib.fhe_comm_create(backend.h, nranks, rank, ctypes.c_char_p(uid), ctypes.byref(h)))
+        self.h, self.nranks, self.rank = h, nranks, rank
+
+    def all_gather(self, dst, src, words, stream=0):
+        """dst (nranks * words device words) receives every rank's `words` words, on this library's stream."""
+        N.check(N.lib.fhe_comm_all_gather(self.h, dst, src, words, stream))
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_comm_destroy(self.h)
+            self.h = None
