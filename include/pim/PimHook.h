@@ -61,6 +61,23 @@ inline const uint64_t *words(const Vec &v) {
   return reinterpret_cast<const uint64_t *>(&v[0]);
 }
 
+/* Streams.  The reference's callers are OpenMP loops (dcrtpoly-impl.h:412; the schemes' loops over ciphertexts), so the
+ * hook is entered from many host threads at once.  Every host thread enqueues on ITS OWN stream of the context's pool
+ * (round robin over the pool), with its own pinned staging block, so the uploads, kernels and downloads of different
+ * threads overlap instead of queueing behind one another on stream 0.  A device copy remembers the stream that wrote
+ * it last; a thread that meets a copy written on another stream waits for that stream first (operands handed from
+ * one thread to another are rare: a ciphertext is normally processed by one thread from start to finish).
+ * FHE_B200_HOOK_ONE_STREAM=1 restores the single-stream behaviour. */
+inline int hook_stream(fhe_ctx *ctx) {
+  static const bool one = [] { const char *e = std::getenv("FHE_B200_HOOK_ONE_STREAM"); return e && *e && *e != '0'; }();
+  if (one) return 0;
+  static std::atomic<int> next{0};
+  thread_local int mine = -1;
+  if (mine < 0) mine = next.fetch_add(1);
+  const int n = fhe_num_streams(ctx);
+  return n > 0 ? mine % n : 0;
+}
+
 struct DeviceBuf {   /* arena block, released on scope exit */
   fhe_ctx *ctx;
   fhe_dptr p = 0;
@@ -75,16 +92,17 @@ inline bool dcrt_eq(PimManager *pim, Towers &a, const Towers &b, int op) {
   const size_t T = a.size(), N = a[0].GetRingDimension(), bytes = N * sizeof(uint64_t);
   auto ring = ring_of(pim, a);
   fhe_ctx *ctx = pim->context();
+  const int S = hook_stream(ctx);
   DeviceBuf da(ctx, T * bytes), db(ctx, T * bytes);
   for (size_t t = 0; t < T; t++) {
-    PimManager::check(fhe_h2d(ctx, da.p + t * bytes, words(a[t].GetValues()), bytes, 0), "pim hook: upload");
-    PimManager::check(fhe_h2d(ctx, db.p + t * bytes, words(b[t].GetValues()), bytes, 0), "pim hook: upload");
+    PimManager::check(fhe_h2d(ctx, da.p + t * bytes, words(a[t].GetValues()), bytes, S), "pim hook: upload");
+    PimManager::check(fhe_h2d(ctx, db.p + t * bytes, words(b[t].GetValues()), bytes, S), "pim hook: upload");
   }
-  PimManager::check(fhe_dcrt_op(ring->handle(), op, da.p, da.p, db.p, 1, 0), "pim hook: dcrt op");
+  PimManager::check(fhe_dcrt_op(ring->handle(), op, da.p, da.p, db.p, 1, S), "pim hook: dcrt op");
   for (size_t t = 0; t < T; t++)
-    PimManager::check(fhe_d2h(ctx, const_cast<uint64_t *>(words(a[t].GetValues())), da.p + t * bytes, bytes, 0),
+    PimManager::check(fhe_d2h(ctx, const_cast<uint64_t *>(words(a[t].GetValues())), da.p + t * bytes, bytes, S),
                       "pim hook: download");
-  PimManager::check(fhe_sync(ctx, 0), "pim hook: sync");
+  PimManager::check(fhe_sync(ctx, S), "pim hook: sync");
   return true;
 }
 
@@ -95,16 +113,17 @@ inline bool dcrt_switch_format(PimManager *pim, Towers &a, bool to_evaluation, F
   const size_t T = a.size(), N = a[0].GetRingDimension(), bytes = N * sizeof(uint64_t);
   auto ring = ring_of(pim, a);
   fhe_ctx *ctx = pim->context();
+  const int S = hook_stream(ctx);
   DeviceBuf d(ctx, T * bytes);
   for (size_t t = 0; t < T; t++)
-    PimManager::check(fhe_h2d(ctx, d.p + t * bytes, words(a[t].GetValues()), bytes, 0), "pim hook: upload");
-  PimManager::check(to_evaluation ? fhe_ntt_forward(ring->handle(), d.p, 1, 0) : fhe_ntt_inverse(ring->handle(), d.p, 1, 0),
+    PimManager::check(fhe_h2d(ctx, d.p + t * bytes, words(a[t].GetValues()), bytes, S), "pim hook: upload");
+  PimManager::check(to_evaluation ? fhe_ntt_forward(ring->handle(), d.p, 1, S) : fhe_ntt_inverse(ring->handle(), d.p, 1, S),
                     "pim hook: transform");
-  PimManager::check(fhe_sync(ctx, 0), "pim hook: sync");
+  PimManager::check(fhe_sync(ctx, S), "pim hook: sync");
   for (size_t t = 0; t < T; t++) {
     auto v = a[t].GetValues();                      /* copy: same length and modulus */
-    PimManager::check(fhe_d2h(ctx, const_cast<uint64_t *>(words(v)), d.p + t * bytes, bytes, 0), "pim hook: download");
-    PimManager::check(fhe_sync(ctx, 0), "pim hook: sync");
+    PimManager::check(fhe_d2h(ctx, const_cast<uint64_t *>(words(v)), d.p + t * bytes, bytes, S), "pim hook: download");
+    PimManager::check(fhe_sync(ctx, S), "pim hook: sync");
     a[t].SetValues(std::move(v), new_format);       /* sets the tower's format without transforming on the CPU */
   }
   return true;
@@ -124,6 +143,7 @@ struct Resident {
   fhe_dptr d = 0;
   size_t towers = 0, n = 0;
   bool device_newer = false;          /* guarded by mu */
+  int stream = 0;                     /* the stream whose work wrote `d` last */
   std::mutex mu;
   ~Resident() { if (d) fhe_free(ctx, d); }
 };
@@ -148,21 +168,29 @@ struct Staging {
     return static_cast<uint64_t *>(p);
   }
 };
-inline Staging &staging() { static Staging s; return s; }
+inline Staging &staging() { thread_local Staging s; return s; }      /* one per host thread: see hook_stream */
+
+/* before `r` is read or written on stream S: wait for the stream that wrote it last, if that is another one */
+inline void join_stream(const std::shared_ptr<Resident> &r, int S) {
+  if (r && r->stream != S) PimManager::check(fhe_sync(r->ctx, r->stream), "pim hook: stream hand-over");
+}
 
 /* makes `towers` resident (uploading them if they are not yet) and returns the device copy */
 template <class Towers>
 inline std::shared_ptr<Resident> ensure_device(PimManager *pim, const Towers &towers, std::shared_ptr<Resident> &res) {
+  const int S = hook_stream(pim->context());
   auto cur = std::atomic_load(&res);
-  if (cur && cur->towers == towers.size() && cur->n == towers[0].GetRingDimension()) return cur;
-  /* first use of this operand: several threads may share it (a key polynomial inside an OpenMP loop), one uploads */
-  static std::mutex create_mu;
-  std::lock_guard<std::mutex> create(create_mu);
+  if (cur && cur->towers == towers.size() && cur->n == towers[0].GetRingDimension()) { join_stream(cur, S); return cur; }
+  /* first use of this operand: several threads may share it (a key polynomial inside an OpenMP loop), one uploads;
+   * the lock is striped by the operand's address so that unrelated operands upload concurrently */
+  static std::mutex create_mu[64];
+  std::lock_guard<std::mutex> create(create_mu[(reinterpret_cast<uintptr_t>(&res) >> 4) & 63]);
   cur = std::atomic_load(&res);
-  if (cur && cur->towers == towers.size() && cur->n == towers[0].GetRingDimension()) return cur;
+  if (cur && cur->towers == towers.size() && cur->n == towers[0].GetRingDimension()) { join_stream(cur, S); return cur; }
   auto r = std::make_shared<Resident>();
   r->ring = ring_of(pim, towers);
   r->ctx = pim->context();
+  r->stream = S;
   r->towers = towers.size();
   r->n = towers[0].GetRingDimension();
   const size_t bytes = r->n * sizeof(uint64_t);
@@ -172,8 +200,8 @@ inline std::shared_ptr<Resident> ensure_device(PimManager *pim, const Towers &to
     std::lock_guard<std::mutex> lock(st.mu);
     uint64_t *h = st.need(r->ctx, r->towers * bytes);
     for (size_t t = 0; t < r->towers; t++) memcpy(h + t * r->n, words(towers[t].GetValues()), bytes);
-    PimManager::check(fhe_h2d(r->ctx, r->d, h, r->towers * bytes, 0), "pim hook: upload");
-    PimManager::check(fhe_sync(r->ctx, 0), "pim hook: sync");   /* the staging block is reused after this */
+    PimManager::check(fhe_h2d(r->ctx, r->d, h, r->towers * bytes, S), "pim hook: upload");
+    PimManager::check(fhe_sync(r->ctx, S), "pim hook: sync");   /* the staging block is reused after this */
   }
   resident_uploads()++;
   std::atomic_store(&res, r);
@@ -187,12 +215,14 @@ inline void sync_host(Towers &towers, const std::shared_ptr<Resident> &res, Form
   std::lock_guard<std::mutex> lock(res->mu);
   if (!res->device_newer) return;
   const size_t bytes = res->n * sizeof(uint64_t);
+  const int S = hook_stream(res->ctx);
+  join_stream(res, S);
   {
     Staging &st = staging();
     std::lock_guard<std::mutex> slock(st.mu);
     uint64_t *h = st.need(res->ctx, res->towers * bytes);
-    PimManager::check(fhe_d2h(res->ctx, h, res->d, res->towers * bytes, 0), "pim hook: download");
-    PimManager::check(fhe_sync(res->ctx, 0), "pim hook: sync");
+    PimManager::check(fhe_d2h(res->ctx, h, res->d, res->towers * bytes, S), "pim hook: download");
+    PimManager::check(fhe_sync(res->ctx, S), "pim hook: sync");
     for (size_t t = 0; t < res->towers; t++) {       /* in place: same length and modulus */
       if (towers[t].IsEmpty()) towers[t].SetValuesToZero();     /* a device result: host storage appears on first read */
       memcpy(const_cast<uint64_t *>(words(towers[t].GetValues())), h + t * res->n, bytes);
@@ -207,7 +237,7 @@ inline void sync_host(Towers &towers, const std::shared_ptr<Resident> &res, Form
  * enqueue-and-return, where only a host read waits) — for measurements */
 inline void finish(fhe_ctx *ctx) {
   static const bool on = [] { const char *e = std::getenv("FHE_B200_HOOK_SYNC"); return e && *e && *e != '0'; }();
-  if (on) PimManager::check(fhe_sync(ctx, 0), "pim hook: sync");
+  if (on) PimManager::check(fhe_sync(ctx, hook_stream(ctx)), "pim hook: sync");
 }
 
 /* a second device copy of the same values (copy construction / assignment of a resident DCRTPoly): HBM to HBM, so a
@@ -216,13 +246,16 @@ inline std::shared_ptr<Resident> clone_resident(const std::shared_ptr<Resident> 
   if (!src) return nullptr;
   auto r = std::make_shared<Resident>();
   std::lock_guard<std::mutex> lock(src->mu);
+  const int S = hook_stream(src->ctx);
+  join_stream(src, S);
+  r->stream = S;
   r->ring = src->ring;
   r->ctx = src->ctx;
   r->towers = src->towers;
   r->n = src->n;
   const size_t bytes = r->towers * r->n * sizeof(uint64_t);
   PimManager::check(fhe_alloc(r->ctx, bytes, &r->d), "pim hook: device buffer");
-  PimManager::check(fhe_d2d(r->ctx, r->d, src->d, bytes, 0), "pim hook: device copy");
+  PimManager::check(fhe_d2d(r->ctx, r->d, src->d, bytes, S), "pim hook: device copy");
   r->device_newer = src->device_newer;
   return r;
 }
@@ -257,7 +290,7 @@ inline std::shared_ptr<PimManager> default_handle() {
   static std::shared_ptr<PimManager> h = [] {
     const char *e = std::getenv("FHE_B200_ATTACH");
     if (!e || !*e || *e == '0') return std::shared_ptr<PimManager>();
-    return std::shared_ptr<PimManager>(PimManager::getPim(4), [](PimManager *) {});
+    return std::shared_ptr<PimManager>(PimManager::getPim(16), [](PimManager *) {});      /* 16 streams: see hook_stream */
   }();
   return h;
 }
@@ -269,9 +302,11 @@ inline bool resident_eq(PimManager *pim, const Towers &a, std::shared_ptr<Reside
   if (!pim || a.empty() || a.size() != b.size()) return false;
   auto da = ensure_device(pim, a, ra);
   auto db = (&a == &b) ? da : ensure_device(pim, b, rb);
-  PimManager::check(fhe_dcrt_op(da->ring->handle(), op, da->d, da->d, db->d, 1, 0), "pim hook: dcrt op");
+  const int S = hook_stream(da->ctx);
+  PimManager::check(fhe_dcrt_op(da->ring->handle(), op, da->d, da->d, db->d, 1, S), "pim hook: dcrt op");
   finish(da->ctx);
   std::lock_guard<std::mutex> lock(da->mu);
+  da->stream = S;
   da->device_newer = true;
   return true;
 }
@@ -284,13 +319,15 @@ inline bool resident_binary(PimManager *pim, const Towers &a, std::shared_ptr<Re
   if (!pim || a.empty() || a.size() != b.size() || out.size() != a.size()) return false;
   auto da = ensure_device(pim, a, ra);
   auto db = (&a == &b) ? da : ensure_device(pim, b, rb);
+  const int S = hook_stream(da->ctx);
   auto r = std::make_shared<Resident>();
   r->ring = da->ring;
   r->ctx = da->ctx;
+  r->stream = S;
   r->towers = da->towers;
   r->n = da->n;
   PimManager::check(fhe_alloc(r->ctx, r->towers * r->n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
-  PimManager::check(fhe_dcrt_op(da->ring->handle(), op, r->d, da->d, db->d, 1, 0), "pim hook: dcrt op");
+  PimManager::check(fhe_dcrt_op(da->ring->handle(), op, r->d, da->d, db->d, 1, S), "pim hook: dcrt op");
   finish(da->ctx);
   r->device_newer = true;
   rout = r;
@@ -301,10 +338,12 @@ template <class Towers>
 inline bool resident_switch_format(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, bool to_evaluation) {
   if (!pim || a.empty()) return false;
   auto da = ensure_device(pim, a, ra);
-  PimManager::check(to_evaluation ? fhe_ntt_forward(da->ring->handle(), da->d, 1, 0) : fhe_ntt_inverse(da->ring->handle(), da->d, 1, 0),
+  const int S = hook_stream(da->ctx);
+  PimManager::check(to_evaluation ? fhe_ntt_forward(da->ring->handle(), da->d, 1, S) : fhe_ntt_inverse(da->ring->handle(), da->d, 1, S),
                     "pim hook: transform");
   finish(da->ctx);
   std::lock_guard<std::mutex> lock(da->mu);
+  da->stream = S;
   da->device_newer = true;
   return true;
 }
@@ -321,11 +360,12 @@ struct CachedPlan {
   std::shared_ptr<PlanLock> lock = std::make_shared<PlanLock>();
 };
 
+/* a plan owns scratch buffers, so every stream gets its own (fhe_b200.h: "use one per stream") */
 inline CachedPlan<PimBasis> basis_for(const std::shared_ptr<PimRing> &from, const std::shared_ptr<PimRing> &to) {
   static std::mutex mu;
-  static std::map<std::pair<PimRing *, PimRing *>, CachedPlan<PimBasis>> cache;
+  static std::map<std::tuple<PimRing *, PimRing *, int>, CachedPlan<PimBasis>> cache;
   std::lock_guard<std::mutex> lock(mu);
-  auto key = std::make_pair(from.get(), to.get());
+  auto key = std::make_tuple(from.get(), to.get(), hook_stream(from->manager()->context()));
   auto it = cache.find(key);
   if (it != cache.end()) return it->second;
   CachedPlan<PimBasis> c;
@@ -336,13 +376,14 @@ inline CachedPlan<PimBasis> basis_for(const std::shared_ptr<PimRing> &from, cons
 
 inline CachedPlan<PimRescale> rescale_for(const std::shared_ptr<PimRing> &ring) {
   static std::mutex mu;
-  static std::map<PimRing *, CachedPlan<PimRescale>> cache;
+  static std::map<std::pair<PimRing *, int>, CachedPlan<PimRescale>> cache;
   std::lock_guard<std::mutex> lock(mu);
-  auto it = cache.find(ring.get());
+  auto key = std::make_pair(ring.get(), hook_stream(ring->manager()->context()));
+  auto it = cache.find(key);
   if (it != cache.end()) return it->second;
   CachedPlan<PimRescale> c;
   c.plan = std::make_shared<PimRescale>(ring);
-  cache.emplace(ring.get(), c);
+  cache.emplace(key, c);
   return c;
 }
 
@@ -352,6 +393,7 @@ inline std::shared_ptr<Resident> new_resident(PimManager *pim, const Towers &tow
   auto r = std::make_shared<Resident>();
   r->ring = ring_of(pim, towers);
   r->ctx = pim->context();
+  r->stream = hook_stream(r->ctx);
   r->towers = towers.size();
   r->n = towers[0].GetRingDimension();
   PimManager::check(fhe_alloc(r->ctx, r->towers * r->n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
@@ -364,9 +406,10 @@ template <class Towers>
 inline bool resident_automorphism(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
                                   std::shared_ptr<Resident> &rout, uint32_t k, int format) {
   if (!pim || a.empty() || out.size() != a.size()) return false;
+  const int S = hook_stream(pim->context());
   auto da = ensure_device(pim, a, ra);
   auto r = new_resident(pim, out);
-  PimManager::check(fhe_automorphism(da->ring->handle(), r->d, da->d, 1, k, format, 0), "pim hook: automorphism");
+  PimManager::check(fhe_automorphism(da->ring->handle(), r->d, da->d, 1, k, format, S), "pim hook: automorphism");
   finish(da->ctx);
   rout = r;
   return true;
@@ -377,11 +420,13 @@ inline bool resident_automorphism(PimManager *pim, const Towers &a, std::shared_
 template <class Towers>
 inline bool resident_rescale(PimManager *pim, const std::shared_ptr<Resident> &full, const Towers &rest,
                              std::shared_ptr<Resident> &res) {
+  const int S = hook_stream(pim->context());
+  join_stream(full, S);
   auto plan = rescale_for(full->ring);
   auto r = new_resident(pim, rest);
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
-    PimManager::check(fhe_drop_last_element_and_scale(plan.plan->handle(), r->d, full->d, 1, 0, 0), "pim hook: rescale");
+    PimManager::check(fhe_drop_last_element_and_scale(plan.plan->handle(), r->d, full->d, 1, 0, S), "pim hook: rescale");
   }
   res = r;      /* the old device copy is released when `full` goes out of scope; stream order keeps it valid until then */
   return true;
@@ -392,12 +437,13 @@ template <class Towers>
 inline bool resident_approx_switch(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, size_t sq, const Towers &out,
                                    std::shared_ptr<Resident> &rout) {
   if (!pim || a.empty() || out.empty() || sq != a.size()) return false;      /* partial source bases stay on the CPU path */
+  const int S = hook_stream(pim->context());
   auto da = ensure_device(pim, a, ra);
   auto r = new_resident(pim, out);
   auto plan = basis_for(da->ring, r->ring);
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
-    PimManager::check(fhe_approx_switch_crt_basis(plan.plan->handle(), r->d, da->d, 1, 0), "pim hook: basis switch");
+    PimManager::check(fhe_approx_switch_crt_basis(plan.plan->handle(), r->d, da->d, 1, S), "pim hook: basis switch");
   }
   rout = r;
   return true;
@@ -408,6 +454,7 @@ template <class Towers>
 inline bool resident_mod_down(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, size_t sq, uint64_t t,
                               const Towers &out, std::shared_ptr<Resident> &rout) {
   if (!pim || a.empty() || sq == 0 || sq >= a.size() || out.size() != sq) return false;
+  const int S = hook_stream(pim->context());
   auto da = ensure_device(pim, a, ra);
   static std::mutex mu;
   static std::map<std::pair<PimRing *, size_t>, std::pair<std::shared_ptr<PimRing>, std::shared_ptr<PimRing>>> views;
@@ -425,6 +472,7 @@ inline bool resident_mod_down(PimManager *pim, const Towers &a, std::shared_ptr<
   auto r = std::make_shared<Resident>();
   r->ring = rq;
   r->ctx = pim->context();
+  r->stream = S;
   r->towers = sq;
   r->n = da->n;
   PimManager::check(fhe_alloc(r->ctx, r->towers * r->n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
@@ -432,7 +480,7 @@ inline bool resident_mod_down(PimManager *pim, const Towers &a, std::shared_ptr<
   auto plan = basis_for(rp, rq);
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
-    PimManager::check(fhe_approx_mod_down(plan.plan->handle(), r->d, da->d, 1, t, 0), "pim hook: mod down");
+    PimManager::check(fhe_approx_mod_down(plan.plan->handle(), r->d, da->d, 1, t, S), "pim hook: mod down");
   }
   rout = r;
   return true;
@@ -444,6 +492,7 @@ template <class Towers>
 inline bool resident_mod_up(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
                             std::shared_ptr<Resident> &rout, int format) {
   if (!pim || a.empty() || out.size() <= a.size()) return false;
+  const int S = hook_stream(pim->context());
   auto da = ensure_device(pim, a, ra);
   auto r = new_resident(pim, out);
   const size_t sq = a.size(), sp = out.size() - sq;
@@ -460,7 +509,7 @@ inline bool resident_mod_up(PimManager *pim, const Towers &a, std::shared_ptr<Re
   auto plan = basis_for(da->ring, rp);
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
-    PimManager::check(fhe_approx_mod_up(plan.plan->handle(), r->d, da->d, 1, format, 0), "pim hook: mod up");
+    PimManager::check(fhe_approx_mod_up(plan.plan->handle(), r->d, da->d, 1, format, S), "pim hook: mod up");
   }
   finish(r->ctx);
   rout = r;
@@ -472,11 +521,13 @@ inline bool resident_mod_up(PimManager *pim, const Towers &a, std::shared_ptr<Re
 template <class Towers>
 inline bool resident_mod_reduce(PimManager *pim, const std::shared_ptr<Resident> &full, const Towers &rest,
                                 std::shared_ptr<Resident> &res, uint64_t t, int format) {
+  const int S = hook_stream(pim->context());
+  join_stream(full, S);
   auto plan = rescale_for(full->ring);
   auto r = new_resident(pim, rest);
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
-    PimManager::check(fhe_mod_reduce(plan.plan->handle(), r->d, full->d, 1, t, format, 0), "pim hook: mod reduce");
+    PimManager::check(fhe_mod_reduce(plan.plan->handle(), r->d, full->d, 1, t, format, S), "pim hook: mod reduce");
   }
   finish(r->ctx);
   res = r;
@@ -500,13 +551,14 @@ template <class Towers, class IntVec>
 inline bool resident_switch_exact(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
                                   std::shared_ptr<Resident> &rout, const IntVec &QHatInvModq) {
   if (!pim || a.empty() || out.empty()) return false;
+  const int S = hook_stream(pim->context());
   auto da = ensure_device(pim, a, ra);
   auto r = new_resident(pim, out);
   auto plan = basis_for(da->ring, r->ring);
   if (!same_hat_inv(plan, QHatInvModq, a.size(), out.size())) return false;
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
-    PimManager::check(fhe_switch_crt_basis(plan.plan->handle(), r->d, da->d, 1, 0), "pim hook: exact basis switch");
+    PimManager::check(fhe_switch_crt_basis(plan.plan->handle(), r->d, da->d, 1, S), "pim hook: exact basis switch");
   }
   finish(r->ctx);
   rout = r;
@@ -520,6 +572,7 @@ inline bool resident_expand(PimManager *pim, const Towers &a, std::shared_ptr<Re
                             std::shared_ptr<Resident> &rout, int format, int result_format, const IntVec &QHatInvModq,
                             bool reverse = false) {      /* reverse: ExpandCRTBasisReverseOrder (:1361-1410), P towers first */
   if (!pim || a.empty() || out.size() <= a.size()) return false;
+  const int S = hook_stream(pim->context());
   auto da = ensure_device(pim, a, ra);
   auto r = new_resident(pim, out);
   const size_t sq = a.size(), sp = out.size() - sq;
@@ -538,10 +591,10 @@ inline bool resident_expand(PimManager *pim, const Towers &a, std::shared_ptr<Re
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
     if (reverse)
-      PimManager::check(fhe_expand_crt_basis_reverse_order(plan.plan->handle(), r->d, da->d, 1, format, result_format, 0),
+      PimManager::check(fhe_expand_crt_basis_reverse_order(plan.plan->handle(), r->d, da->d, 1, format, result_format, S),
                         "pim hook: expand basis (reverse order)");
     else
-      PimManager::check(fhe_expand_crt_basis(plan.plan->handle(), r->d, da->d, 1, format, result_format, 0), "pim hook: expand basis");
+      PimManager::check(fhe_expand_crt_basis(plan.plan->handle(), r->d, da->d, 1, format, result_format, S), "pim hook: expand basis");
   }
   finish(r->ctx);
   rout = r;
@@ -558,6 +611,7 @@ inline bool resident_fast_expand_pl_over_q(PimManager *pim, const Towers &a, std
                                            const IntVec &PlHatInvModp) {
   const size_t sq = a.size(), spl = out.size() / 2, sql = out.size() - spl;
   if (!pim || a.empty() || spl == 0 || sql != spl || mPlQHatInvModq.size() < sq || qInvModp.size() < sq) return false;
+  const int S = hook_stream(pim->context());
   auto da = ensure_device(pim, a, ra);
   auto r = new_resident(pim, out);
   static std::mutex mu;
@@ -566,7 +620,7 @@ inline bool resident_fast_expand_pl_over_q(PimManager *pim, const Towers &a, std
     CachedPlan<PimBasis> plan;
     std::vector<uint64_t> neg;
   };
-  static std::map<std::tuple<PimRing *, PimRing *, const void *>, Entry> cache;
+  static std::map<std::tuple<PimRing *, PimRing *, const void *, int>, Entry> cache;
   std::shared_ptr<PimRing> rql, rpl;
   Entry e;
   {
@@ -579,7 +633,7 @@ inline bool resident_fast_expand_pl_over_q(PimManager *pim, const Towers &a, std
     rpl = it->second.second;
     std::vector<uint64_t> neg(sq);
     for (size_t i = 0; i < sq; i++) neg[i] = mPlQHatInvModq[i].ConvertToInt();
-    auto key = std::make_tuple(da->ring.get(), rpl.get(), (const void *)&mPlQHatInvModq[0]);
+    auto key = std::make_tuple(da->ring.get(), rpl.get(), (const void *)&mPlQHatInvModq[0], S);
     auto ce = cache.find(key);
     if (ce == cache.end() || ce->second.neg != neg) {
       std::vector<uint64_t> flat;
@@ -601,7 +655,7 @@ inline bool resident_fast_expand_pl_over_q(PimManager *pim, const Towers &a, std
   {
     std::lock_guard<std::mutex> l1(e.plan.lock->mu);
     std::lock_guard<std::mutex> l2(back.lock->mu);
-    PimManager::check(fhe_fast_expand_crt_basis_pl_over_q(e.plan.plan->handle(), back.plan->handle(), r->d, da->d, 1, 0),
+    PimManager::check(fhe_fast_expand_crt_basis_pl_over_q(e.plan.plan->handle(), back.plan->handle(), r->d, da->d, 1, S),
                       "pim hook: fast expand P over Q");
   }
   finish(r->ctx);
@@ -623,6 +677,7 @@ inline bool resident_tower_scale(PimManager *pim, int mode, const Towers &a, std
   if (!pim || a.empty() || T == 0 || c.size() < sl) return false;
   if (mode == 0 ? a.size() > T : a.size() != T + 1) return false;
   if (times && a.size() != T) return false;
+  const int S = hook_stream(pim->context());
   auto da = ensure_device(pim, a, ra);
   auto r = new_resident(pim, out);
   struct Entry {
@@ -653,10 +708,10 @@ inline bool resident_tower_scale(PimManager *pim, int mode, const Towers &a, std
   {
     std::lock_guard<std::mutex> lock(e.plan.lock->mu);
     if (mode == 0)
-      PimManager::check(fhe_expand_crt_basis_ql_hat(e.plan.plan->handle(), (uint32_t)sl, r->d, da->d, 1, 0),
+      PimManager::check(fhe_expand_crt_basis_ql_hat(e.plan.plan->handle(), (uint32_t)sl, r->d, da->d, 1, S),
                         "pim hook: expand basis (QlHat)");
     else
-      PimManager::check(fhe_scale_and_round_p_over_q(e.plan.plan->handle(), r->d, da->d, 1, 0), "pim hook: scale and round P over Q");
+      PimManager::check(fhe_scale_and_round_p_over_q(e.plan.plan->handle(), r->d, da->d, 1, S), "pim hook: scale and round P over Q");
   }
   rout = r;
   return true;
@@ -670,6 +725,7 @@ inline bool resident_scale_round(PimManager *pim, const Towers &a, std::shared_p
                                  std::shared_ptr<Resident> &rout, bool out_last, const std::vector<double> &frac, const Rows &modo) {
   const size_t so = out.size();
   if (!pim || a.empty() || so == 0 || so >= a.size() || frac.size() != a.size() - so || modo.size() != so) return false;
+  const int S = hook_stream(pim->context());
   auto da = ensure_device(pim, a, ra);
   struct Entry {
     std::shared_ptr<PimScaleRound> plan;
@@ -677,11 +733,11 @@ inline bool resident_scale_round(PimManager *pim, const Towers &a, std::shared_p
     std::vector<double> frac;
   };
   static std::mutex mu;
-  static std::map<std::tuple<PimRing *, size_t, bool, const double *>, Entry> cache;
+  static std::map<std::tuple<PimRing *, size_t, bool, const double *, int>, Entry> cache;
   Entry e;
   {
     std::lock_guard<std::mutex> lock(mu);
-    auto key = std::make_tuple(da->ring.get(), so, out_last, frac.data());
+    auto key = std::make_tuple(da->ring.get(), so, out_last, frac.data(), S);
     auto it = cache.find(key);
     if (it == cache.end() || it->second.frac != frac) {
       std::vector<uint64_t> flat;
@@ -701,13 +757,14 @@ inline bool resident_scale_round(PimManager *pim, const Towers &a, std::shared_p
   auto r = std::make_shared<Resident>();
   r->ring = e.plan->Out();
   r->ctx = pim->context();
+  r->stream = S;
   r->towers = so;
   r->n = da->n;
   PimManager::check(fhe_alloc(r->ctx, r->towers * r->n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
   r->device_newer = true;
   {
     std::lock_guard<std::mutex> lock(e.lock->mu);
-    PimManager::check(fhe_scale_and_round(e.plan->handle(), r->d, da->d, 1, 0), "pim hook: scale and round");
+    PimManager::check(fhe_scale_and_round(e.plan->handle(), r->d, da->d, 1, S), "pim hook: scale and round");
   }
   finish(r->ctx);
   rout = r;

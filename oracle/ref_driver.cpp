@@ -55,7 +55,7 @@ int ref_polys_set_pim(ref_polys* p, int on) {
 #ifdef FHE_HOOKED
     try {
         std::shared_ptr<PimManager> h;
-        if (on) h = std::shared_ptr<PimManager>(PimManager::getPim(4), [](PimManager*) {});
+        if (on) h = std::shared_ptr<PimManager>(PimManager::getPim(16), [](PimManager*) {});      // 16 streams, one per host thread (pim/PimHook.h)
         for (auto& poly : p->v) poly.SetPim(h);
         return 0;
     }
@@ -138,6 +138,20 @@ void ref_polys_store(const ref_polys* p, uint64_t* out) {
         for (uint32_t t = 0; t < c->T; t++) {
             const auto& vals = p->v[b].GetElementAtIndex(t).GetValues();
             uint64_t* dst    = out + (b * c->T + t) * (size_t)c->N;
+            for (uint32_t j = 0; j < c->N; j++)
+                dst[j] = vals[j].ConvertToInt();
+        }
+}
+// the same with an omp-for over the batch (static schedule: poly i is read by the thread that ran ref_polys_op /
+// ref_polys_switch_format on it with the same thread count, so in the hooked build its download rides that thread's stream)
+void ref_polys_store_mt(const ref_polys* p, uint64_t* out, int threads) {
+    ref_ctx* c = p->ctx;
+    if (threads <= 1) { ref_polys_store(p, out); return; }
+#pragma omp parallel for num_threads(threads) schedule(static)
+    for (long b = 0; b < (long)p->v.size(); b++)
+        for (uint32_t t = 0; t < c->T; t++) {
+            const auto& vals = p->v[b].GetElementAtIndex(t).GetValues();
+            uint64_t* dst    = out + ((size_t)b * c->T + t) * (size_t)c->N;
             for (uint32_t j = 0; j < c->N; j++)
                 dst[j] = vals[j].ConvertToInt();
         }

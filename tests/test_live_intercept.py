@@ -547,3 +547,40 @@ def test_default_attach_runs_unmodified_callers_on_the_device():
     r = subprocess.run([sys.executable, "-c", "from tests import test_live_intercept as t; t._attach_child()"], cwd=root, env=env,
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "attach-child ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+@pytest.mark.gpu
+def test_intercept_from_many_host_threads(hooked, oracle):
+    """The reference's callers are OpenMP loops: with the handle attached, eight host threads run a chain of operators on
+    their own polynomials at once, each enqueueing on its own stream (pim/PimHook.h hook_stream); a polynomial that one
+    thread produced is then read by another (schedule differs between the operator loop and the store).  Results must
+    equal the CPU path."""
+    H = hooked
+    H.ref_polys_store_mt.argtypes = [vp, vp, ci]
+    n, towers, batch, threads = 1 << 13, 5, 48, 8
+    q, psi = oracle.gen_params(60, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    a, b = oracle.fill_ring(batch, n, q, 71), oracle.fill_ring(batch, n, q, 72)
+    want = a
+    for _ in range(3):
+        want = octx.elementwise(0, want, b)
+        want = octx.elementwise(2, want, b)
+        want = octx.ntt(octx.ntt(want, inverse=True), inverse=False)
+        want = octx.elementwise(1, want, b)
+    ctx = H.ref_ctx_create(n, towers, p(q), p(psi))
+    try:
+        for trial in range(3):
+            ha, hb = H.ref_polys_load(ctx, p(a), batch, 0), H.ref_polys_load(ctx, p(b), batch, 0)
+            assert H.ref_polys_set_pim(ha, 1) == 0, H.ref_last_error()
+            for _ in range(3):
+                assert H.ref_polys_op(ha, hb, 0, threads) >= 0, H.ref_last_error()
+                H.ref_polys_op(ha, hb, 2, threads)
+                H.ref_polys_switch_format(ha, threads)
+                H.ref_polys_switch_format(ha, threads)
+                H.ref_polys_op(ha, hb, 1, threads)
+            res = np.empty_like(a)
+            H.ref_polys_store_mt(ha, p(res), 3 if trial else threads)      # another thread count: streams are handed over
+            assert np.array_equal(res, want), f"trial {trial}"
+            H.ref_polys_free(ha); H.ref_polys_free(hb)
+    finally:
+        H.ref_ctx_destroy(ctx)

@@ -531,6 +531,7 @@ extern "C" int fhe_ring_create(fhe_ctx* ctx, uint32_t N, uint32_t T, const uint6
     int rc = ctx->arena.alloc(sizeof(TowerMod) * T, &r->d_mods);
     if (rc) { fhe_ring_destroy(r); return rc; }
     cudaError_t e = cudaMemcpy(r->d_mods, mods.data(), sizeof(TowerMod) * T, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(cudaStreamLegacy);      // pageable source: see upload()
     if (e != cudaSuccess) { fhe_ring_destroy(r); return fail(FHE_ECUDA, "upload moduli: %s", cudaGetErrorString(e)); }
     r->dev.mods = (const TowerMod*)r->d_mods;
 
@@ -579,7 +580,8 @@ extern "C" int fhe_ring_create(fhe_ctx* ctx, uint32_t N, uint32_t T, const uint6
             }
             if ((e = cudaMemcpy(r->d_twF, hF.data(), tabBytes, cudaMemcpyHostToDevice)) != cudaSuccess ||
                 (e = cudaMemcpy(r->d_twI, hI.data(), tabBytes, cudaMemcpyHostToDevice)) != cudaSuccess ||
-                (e = cudaMemcpy(r->d_invc, hC.data(), (size_t)T * 32, cudaMemcpyHostToDevice)) != cudaSuccess) {
+                (e = cudaMemcpy(r->d_invc, hC.data(), (size_t)T * 32, cudaMemcpyHostToDevice)) != cudaSuccess ||
+                (e = cudaStreamSynchronize(cudaStreamLegacy)) != cudaSuccess) {
                 fhe_ring_destroy(r);
                 return fail(FHE_ECUDA, "upload twiddle tables: %s", cudaGetErrorString(e));
             }
@@ -918,6 +920,10 @@ int upload(fhe_ctx* ctx, const std::vector<T>& h, void** d) {
         cudaDeviceSynchronize();      // a table being replaced may still be read by launches on the (non-blocking) pool streams
     }
     cudaError_t e = cudaMemcpy(*d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
+    // A copy from pageable memory returns once the data sits in the driver's staging buffer; the DMA may still be in
+    // flight, and the (non-blocking) pool streams do not wait for the legacy stream.  Wait for it here: the caller
+    // launches on a pool stream next.
+    if (e == cudaSuccess) e = cudaStreamSynchronize(cudaStreamLegacy);
     return e == cudaSuccess ? FHE_OK : fail(FHE_ECUDA, "upload constants: %s", cudaGetErrorString(e));
 }
 
