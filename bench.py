@@ -710,6 +710,20 @@ def ntt_extra(pkg, be):
         out["approx_mod_down_n65536_q30_p10_b16"] = {"ms": ms, "polys_per_s": batch / (ms * 1e-3)}
         ms = timed(lambda: plan.drop_last_element_and_scale(dr, dqp, batch, 0))
         out["drop_last_element_and_scale_n65536_t40_b16"] = {"ms": ms, "polys_per_s": batch / (ms * 1e-3)}
+        # hybrid key switching (CKKS relinearisation / rotation shape): 30 towers of Ql, 10 of P, 3 digits of 10 towers
+        ks = pkg.KeySwitch(ring, sq, 10)
+        kb, ka = be.alloc(ks.digits * (sq + sp) * n * 8), be.alloc(ks.digits * (sq + sp) * n * 8)
+        ring.fill_uniform(kb, ks.digits, 20260033); ring.fill_uniform(ka, ks.digits, 20260034)
+        o0, o1 = be.alloc(wq * 8), be.alloc(wq * 8)
+        rq.fill_uniform(dq, batch, 20260030)
+        ms = timed(lambda: ks(o0, o1, dq, kb, ka, batch, 0))
+        out["keyswitch_hybrid_n65536_ql30_p10_alpha10_b16"] = {
+            "ms": ms, "key_switches_per_s": batch / (ms * 1e-3),
+            "note": "KeySwitchHYBRID::KeySwitchCore: 3 digits x (INTT, ApproxSwitchCRTBasis to the complement basis, NTT), fused "
+                    "inner product with the key over 40 towers, 2 x ApproxModDown; device-resident"}
+        ks.close()
+        for b_ in (kb, ka, o0, o1):
+            be.free(b_)
         # HPSPOVERQ tails (tower_scale_kernel): HBM-bound, 8 B in + 8 B out per coefficient per tower (+ the extra tower)
         rq1 = pkg.RingView(ring, 0, sq + sp - 1)
         kq = [int(v) // 3 for v in q[:sq + sp - 1]]

@@ -265,6 +265,30 @@ int fhe_drop_last_element_and_scale(fhe_rescale* plan, fhe_dptr dst, fhe_dptr sr
  * [-t^-1]_{ql} and [t]_{q_i} (bgvrns-cryptoparameters.cpp:91-99) are derived here.  Format is preserved. */
 int fhe_mod_reduce(fhe_rescale* plan, fhe_dptr dst, fhe_dptr src, size_t batch, uint64_t t, int format, int stream);
 
+/* ---- hybrid key switching (CKKS / BGV relinearisation and rotations) --------------------------- */
+/* KeySwitchHYBRID (src/pke/lib/keyswitch/keyswitch-hybrid.cpp:324-480) at one level as a device composition.
+ * ring_qlp: the size_ql current towers of Q followed by the towers of P; alpha: towers per digit
+ * (CryptoParametersRNS::GetNumPerPartQ); digits = ceil(size_ql / alpha), the last one may be shorter.  The digit
+ * tables ([(Q_j/q_i)^-1]_{q_i}, [Q_j/q_i]_{p}, rns-cryptoparameters.cpp:289-340) and [P^-1]_{q_i} are derived from
+ * the moduli.  The ring must outlive the plan; a plan keeps scratch buffers, so use one per stream.
+ *   fhe_keyswitch_precompute = EvalKeySwitchPrecomputeCore (:330-420): c over Ql [batch][size_ql][N], EVALUATION ->
+ *       digits [digits][batch][T][N], EVALUATION (per digit: INTT of its towers, ApproxSwitchCRTBasis to the
+ *       complement basis, NTT, the digit's own towers copied in).
+ *   fhe_keyswitch_inner = EvalFastKeySwitchCoreExt (:442-480): ctilda0 = sum_j digits[j] * evk_b[j],
+ *       ctilda1 = sum_j digits[j] * evk_a[j], one fused pass; the key polys are given over the towers of ring_qlp
+ *       ([digits][T][N], EVALUATION: towers i < size_ql and size_q.. of the scheme's key, :463-476).
+ *   fhe_keyswitch_hybrid = KeySwitchCore / EvalFastKeySwitchCore (:324-328, 422-440): the two above, then
+ *       ApproxModDown of both halves; ct0, ct1 over Ql [batch][size_ql][N]; t = 0 CKKS, t > 0 BGV. */
+typedef struct fhe_keyswitch fhe_keyswitch;
+int fhe_keyswitch_create(fhe_ring* ring_qlp, uint32_t size_ql, uint32_t alpha, fhe_keyswitch** out);
+int fhe_keyswitch_destroy(fhe_keyswitch* plan);
+uint32_t fhe_keyswitch_digits(const fhe_keyswitch* plan);
+int fhe_keyswitch_precompute(fhe_keyswitch* plan, fhe_dptr digits, fhe_dptr c, size_t batch, int stream);
+int fhe_keyswitch_inner(fhe_keyswitch* plan, fhe_dptr ctilda0, fhe_dptr ctilda1, fhe_dptr digits, fhe_dptr evk_b,
+                        fhe_dptr evk_a, size_t batch, int stream);
+int fhe_keyswitch_hybrid(fhe_keyswitch* plan, fhe_dptr ct0, fhe_dptr ct1, fhe_dptr c, fhe_dptr evk_b, fhe_dptr evk_a,
+                         size_t batch, uint64_t t, int stream);
+
 /* ---- wire format of device-resident polys ---------------------------------------------------- */
 /* The reference's binary serialisation of one DCRTPoly — Serial::Serialize(poly, os, SerType::BINARY)
  * (utils/serial.h:99-103): a cereal portable-binary stream of DCRTPolyImpl::save (dcrtpoly.h:349-354) over

@@ -821,6 +821,93 @@ void orc_scale_and_round(uint64_t* out, const uint64_t* in, size_t B, uint32_t N
     free(mu);
 }
 
+/* ---- hybrid key switching (KeySwitchHYBRID, src/pke/lib/keyswitch/keyswitch-hybrid.cpp) ----------------------------
+ * QlP = the ring over the sizeQl current towers of Q followed by the sizeP towers of P.  Digits of alpha towers
+ * (the last may be shorter), numPart = ceil(sizeQl / alpha)  (:345-348, without the cap at GetNumberOfQPartitions:
+ * the caller passes the alpha of its parameter set, for which the cap never binds at this level).
+ * orc_keyswitch_precompute = EvalKeySwitchPrecomputeCore (:330-420): digits [numPart][B][sizeQl+sizeP][N], EVALUATION.
+ *   per digit: its towers of c -> COEFFICIENT (:392-393) -> ApproxSwitchCRTBasis to the complement basis (the other
+ *   towers of Ql, then P) with the tables of the (truncated) digit basis (:396-402; rns-cryptoparameters.cpp:289-340
+ *   builds exactly orc_switch_tables of those moduli) -> EVALUATION (:404) -> complement towers and the digit's own
+ *   stored towers put at their places (:406-418).
+ * orc_keyswitch_inner = EvalFastKeySwitchCoreExt (:442-480): cTilda0 = sum_j digit_j * b_j, cTilda1 = sum_j digit_j * a_j
+ *   tower by tower; the key polys are given over the same sizeQl+sizeP towers ([numPart][sizeQl+sizeP][N]: the caller
+ *   picks towers i < sizeQl and sizeQ.. of its key, :463-476).
+ * orc_keyswitch_hybrid = KeySwitchCore / EvalFastKeySwitchCore (:324-328, 422-440): the two ApproxModDown to Ql. */
+static orc_ctx* sub_ctx(const orc_ctx* c, const uint32_t* idx, uint32_t cnt) {
+    uint64_t q[256], psi[256];
+    for (uint32_t k = 0; k < cnt; k++) { q[k] = c->q[idx[k]]; psi[k] = c->psi[idx[k]]; }
+    return orc_ctx_create(c->N, cnt, q, psi);
+}
+
+uint32_t orc_keyswitch_digits(uint32_t sizeQl, uint32_t alpha) { return (sizeQl + alpha - 1) / alpha; }
+
+void orc_keyswitch_precompute(const orc_ctx* QlP, uint32_t sizeQl, uint32_t alpha, uint64_t* digits, const uint64_t* c, size_t B) {
+    const uint32_t N = QlP->N, T = QlP->T, np = orc_keyswitch_digits(sizeQl, alpha);
+    for (uint32_t part = 0; part < np; part++) {
+        const uint32_t s = alpha * part, e = s + alpha < sizeQl ? s + alpha : sizeQl, sp = e - s, sc = T - sp;
+        uint32_t pidx[256], cidx[256];
+        for (uint32_t k = 0; k < sp; k++) pidx[k] = s + k;
+        for (uint32_t k = 0, i = 0; i < T; i++) if (i < s || i >= e) cidx[k++] = i;
+        orc_ctx *part_ctx = sub_ctx(QlP, pidx, sp), *compl_ctx = sub_ctx(QlP, cidx, sc);
+        uint64_t* coef = (uint64_t*)malloc(B * sp * (size_t)N * 8);
+        uint64_t* comp = (uint64_t*)malloc(B * sc * (size_t)N * 8);
+        uint64_t* hi = (uint64_t*)malloc(8 * sp);
+        uint64_t* hm = (uint64_t*)malloc(8 * (size_t)sp * sc);
+        towers_copy(coef, sp, 0, c, sizeQl, s, sp, B, N);
+        orc_dcrt_ntt(part_ctx, 1, coef, B, 0);
+        orc_switch_tables(part_ctx->q, sp, compl_ctx->q, sc, hi, hm);
+        orc_approx_switch(comp, coef, B, N, part_ctx->q, sp, compl_ctx->q, sc, hi, hm);
+        orc_dcrt_ntt(compl_ctx, 0, comp, B, 0);
+        uint64_t* d = digits + (size_t)part * B * T * N;
+        towers_copy(d, T, 0, comp, sc, 0, s, B, N);                       /* towers below the digit */
+        towers_copy(d, T, s, c, sizeQl, s, sp, B, N);                     /* the digit's own towers, as stored */
+        towers_copy(d, T, e, comp, sc, s, T - e, B, N);                   /* the rest of Ql, then P */
+        free(coef); free(comp); free(hi); free(hm);
+        orc_ctx_destroy(part_ctx); orc_ctx_destroy(compl_ctx);
+    }
+}
+
+void orc_keyswitch_inner(const orc_ctx* QlP, uint32_t np, uint64_t* c0, uint64_t* c1, const uint64_t* digits,
+                         const uint64_t* evk_b, const uint64_t* evk_a, size_t B) {
+    const uint32_t N = QlP->N, T = QlP->T;
+    long units = (long)(B * T);
+#pragma omp parallel for schedule(static)
+    for (long u = 0; u < units; u++) {
+        const uint32_t t = (uint32_t)(u % T);
+        const uint64_t q = QlP->q[t], mu = orc_compute_mu(q);
+        uint64_t *o0 = c0 + (size_t)u * N, *o1 = c1 + (size_t)u * N;
+        for (uint32_t n = 0; n < N; n++) o0[n] = o1[n] = 0;               /* DCRTPoly(paramsQlP, EVALUATION, true) */
+        for (uint32_t j = 0; j < np; j++) {
+            const uint64_t* d = digits + ((size_t)j * B * T + (size_t)u) * N;
+            const uint64_t* kb = evk_b + ((size_t)j * T + t) * N;
+            const uint64_t* ka = evk_a + ((size_t)j * T + t) * N;
+            for (uint32_t n = 0; n < N; n++) {
+                o0[n] = orc_modadd_fast(o0[n], orc_modmul_barrett(d[n], kb[n], q, mu), q);
+                o1[n] = orc_modadd_fast(o1[n], orc_modmul_barrett(d[n], ka[n], q, mu), q);
+            }
+        }
+    }
+}
+
+void orc_keyswitch_hybrid(const orc_ctx* QlP, uint32_t sizeQl, uint32_t alpha, uint64_t* ct0, uint64_t* ct1, const uint64_t* c,
+                          const uint64_t* evk_b, const uint64_t* evk_a, size_t B, uint64_t t) {
+    const uint32_t N = QlP->N, T = QlP->T, np = orc_keyswitch_digits(sizeQl, alpha), sizeP = T - sizeQl;
+    uint64_t* digits = (uint64_t*)malloc((size_t)np * B * T * N * 8);
+    uint64_t* c0 = (uint64_t*)malloc(B * T * (size_t)N * 8);
+    uint64_t* c1 = (uint64_t*)malloc(B * T * (size_t)N * 8);
+    orc_keyswitch_precompute(QlP, sizeQl, alpha, digits, c, B);
+    orc_keyswitch_inner(QlP, np, c0, c1, digits, evk_b, evk_a, B);
+    uint32_t qi[256], pi[256];
+    for (uint32_t k = 0; k < sizeQl; k++) qi[k] = k;
+    for (uint32_t k = 0; k < sizeP; k++) pi[k] = sizeQl + k;
+    orc_ctx *Q = sub_ctx(QlP, qi, sizeQl), *P = sub_ctx(QlP, pi, sizeP);
+    orc_approx_mod_down(Q, P, ct0, c0, B, t);
+    orc_approx_mod_down(Q, P, ct1, c1, B, t);
+    orc_ctx_destroy(Q); orc_ctx_destroy(P);
+    free(digits); free(c0); free(c1);
+}
+
 int orc_max_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

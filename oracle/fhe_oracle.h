@@ -77,6 +77,13 @@ void     orc_ctx_destroy(orc_ctx* c);
 void     orc_dcrt_elementwise(const orc_ctx* c, int op, uint64_t* dst, const uint64_t* a,
                               const uint64_t* b, size_t B, int nthreads);
 void     orc_dcrt_ntt(const orc_ctx* c, int inverse, uint64_t* x, size_t B, int nthreads);
+/* hybrid key switching (keyswitch-hybrid.cpp:324-480); QlP = sizeQl towers of Q then P; digits of alpha towers */
+uint32_t orc_keyswitch_digits(uint32_t sizeQl, uint32_t alpha);
+void     orc_keyswitch_precompute(const orc_ctx* QlP, uint32_t sizeQl, uint32_t alpha, uint64_t* digits, const uint64_t* c, size_t B);
+void     orc_keyswitch_inner(const orc_ctx* QlP, uint32_t np, uint64_t* c0, uint64_t* c1, const uint64_t* digits,
+                             const uint64_t* evk_b, const uint64_t* evk_a, size_t B);
+void     orc_keyswitch_hybrid(const orc_ctx* QlP, uint32_t sizeQl, uint32_t alpha, uint64_t* ct0, uint64_t* ct1, const uint64_t* c,
+                              const uint64_t* evk_b, const uint64_t* evk_a, size_t B, uint64_t t);
 int      orc_max_threads(void);
 
 /* ---- automorphism X -> X^k, k odd ----

@@ -866,6 +866,134 @@ ref_polys* ref_polys_deserialize(ref_ctx* c, const uint8_t* bytes, size_t len) {
     }
 }
 
+// ---- hybrid key switching on the reference's own DCRTPoly -----------------------------------------------------------
+// The statements of KeySwitchHYBRID::EvalKeySwitchPrecomputeCore / EvalFastKeySwitchCoreExt / EvalFastKeySwitchCore
+// (src/pke/lib/keyswitch/keyswitch-hybrid.cpp:330-480) — src/pke itself is not compiled here — with the tables the
+// scheme parameters would hold (rns-cryptoparameters.cpp:236-340: the products run over the (truncated) digit basis,
+// i.e. make_switch_tables of its moduli).  c over Ql (EVALUATION); QlP = Ql towers then P; the key polys evk_b / evk_a
+// are given over the towers of QlP ([numPart][T][N], EVALUATION).  out[0], out[1] over Ql.
+static std::shared_ptr<ILDCRTParams<BigInteger>> sub_params(const ref_ctx* c, const std::vector<uint32_t>& idx) {
+    std::vector<NativeInteger> moduli, roots;
+    for (uint32_t i : idx) {
+        moduli.push_back(c->params->GetParams()[i]->GetModulus());
+        roots.push_back(c->params->GetParams()[i]->GetRootOfUnity());
+    }
+    return std::make_shared<ILDCRTParams<BigInteger>>(2 * c->N, moduli, roots);
+}
+static std::vector<NativeInteger> moduli_of_params(const std::shared_ptr<ILDCRTParams<BigInteger>>& p) {
+    std::vector<NativeInteger> m;
+    for (auto& tp : p->GetParams()) m.push_back(tp->GetModulus());
+    return m;
+}
+
+int ref_keyswitch_hybrid(const ref_polys* c, ref_ctx* QlP, uint32_t sizeQl, uint32_t alpha, const uint64_t* evk_b,
+                         const uint64_t* evk_a, uint64_t t, ref_polys** out, uint64_t* digits_out) {
+    int rc = 0;
+    std::string err;
+    serial_omp([&] {
+        try {
+            ref_ctx* Ql       = c->ctx;
+            const uint32_t T = QlP->T, N = QlP->N, sizeP = T - sizeQl;
+            const uint32_t numPartQl = (sizeQl + alpha - 1) / alpha;
+            auto paramsQlP = QlP->params;
+            std::vector<uint32_t> pidx;
+            for (uint32_t i = sizeQl; i < T; i++) pidx.push_back(i);
+            auto paramsP = sub_params(QlP, pidx);
+            // key polys over QlP
+            auto load_key = [&](const uint64_t* data, uint32_t j) {
+                DCRTPoly k(paramsQlP, Format::EVALUATION, true);
+                for (uint32_t i = 0; i < T; i++) {
+                    auto tp = paramsQlP->GetParams()[i];
+                    NativeVector vec(N, tp->GetModulus());
+                    const uint64_t* src = data + ((size_t)j * T + i) * N;
+                    for (uint32_t n = 0; n < N; n++) vec[n] = NativeInteger(src[n]);
+                    NativePoly np(tp, Format::EVALUATION, false);
+                    np.SetValues(std::move(vec), Format::EVALUATION);
+                    k.SetElementAtIndex(i, std::move(np));
+                }
+                return k;
+            };
+            std::vector<DCRTPoly> bv, av;
+            for (uint32_t j = 0; j < numPartQl; j++) { bv.push_back(load_key(evk_b, j)); av.push_back(load_key(evk_a, j)); }
+            // ApproxModDown tables (rns-cryptoparameters.cpp:190-229)
+            auto mq = moduli_of(Ql), mp = moduli_of_params(paramsP);
+            auto tb = make_switch_tables(mp, mq);
+            BigInteger modP(1);
+            for (auto& pj : mp) modP *= BigInteger(pj);
+            std::vector<NativeInteger> PInv(mq.size()), PInvPrecon(mq.size()), tInv(mp.size()), tInvPrecon(mp.size()), tModqPrecon(mq.size());
+            for (size_t i = 0; i < mq.size(); i++) {
+                PInv[i]       = modP.ModInverse(BigInteger(mq[i])).ConvertToInt();
+                PInvPrecon[i] = PInv[i].PrepModMulConst(mq[i]);
+                if (t) tModqPrecon[i] = NativeInteger(t).PrepModMulConst(mq[i]);
+            }
+            if (t)
+                for (size_t j = 0; j < mp.size(); j++) {
+                    tInv[j]       = NativeInteger(t).ModInverse(mp[j]);
+                    tInvPrecon[j] = tInv[j].PrepModMulConst(mp[j]);
+                }
+            for (int k = 0; k < 2; k++) out[k] = new ref_polys{Ql, {}};
+            size_t bi = 0;
+            for (const DCRTPoly& cpoly : c->v) {
+                // ---- EvalKeySwitchPrecomputeCore, :352-417 ----
+                std::vector<DCRTPoly> partsCt(numPartQl), partsCtCompl(numPartQl), partsCtExt(numPartQl);
+                std::vector<std::shared_ptr<ILDCRTParams<BigInteger>>> partParams(numPartQl), complParams(numPartQl);
+                for (uint32_t part = 0; part < numPartQl; part++) {
+                    uint32_t start = alpha * part, sizePartQl = std::min(alpha, sizeQl - start);
+                    std::vector<uint32_t> idx, cidx;
+                    for (uint32_t i = 0; i < sizePartQl; i++) idx.push_back(start + i);
+                    for (uint32_t i = 0; i < T; i++)
+                        if (i < start || i >= start + sizePartQl) cidx.push_back(i);
+                    partParams[part]  = sub_params(QlP, idx);
+                    complParams[part] = sub_params(QlP, cidx);
+                    partsCt[part]     = DCRTPoly(partParams[part], Format::EVALUATION, true);
+                    for (uint32_t i = 0, id = start; i < sizePartQl; i++, id++)
+                        partsCt[part].SetElementAtIndex(i, cpoly.GetElementAtIndex(id));
+                }
+                for (uint32_t part = 0; part < numPartQl; part++) {
+                    auto partCtClone = partsCt[part].Clone();
+                    partCtClone.SetFormat(Format::COEFFICIENT);
+                    uint32_t sizePartQl = partsCt[part].GetNumOfElements();
+                    auto tbl = make_switch_tables(moduli_of_params(partParams[part]), moduli_of_params(complParams[part]));
+                    partsCtCompl[part] = partCtClone.ApproxSwitchCRTBasis(partParams[part], complParams[part], tbl.hatInv,
+                                                                          tbl.hatInvPrecon, tbl.hatModp, tbl.mu);
+                    partsCtCompl[part].SetFormat(Format::EVALUATION);
+                    partsCtExt[part] = DCRTPoly(paramsQlP, Format::EVALUATION, true);
+                    uint32_t startPartIdx = alpha * part, endPartIdx = startPartIdx + sizePartQl;
+                    for (uint32_t i = 0; i < startPartIdx; i++)
+                        partsCtExt[part].SetElementAtIndex(i, partsCtCompl[part].GetElementAtIndex(i));
+                    for (uint32_t i = startPartIdx, id = 0; i < endPartIdx; i++, id++)
+                        partsCtExt[part].SetElementAtIndex(i, partsCt[part].GetElementAtIndex(id));
+                    for (uint32_t i = endPartIdx; i < T; ++i)
+                        partsCtExt[part].SetElementAtIndex(i, partsCtCompl[part].GetElementAtIndex(i - sizePartQl));
+                    if (digits_out)
+                        for (uint32_t i = 0; i < T; i++) {
+                            const auto& vals = partsCtExt[part].GetElementAtIndex(i).GetValues();
+                            uint64_t* dst    = digits_out + (((size_t)part * c->v.size() + bi) * T + i) * N;
+                            for (uint32_t n = 0; n < N; n++) dst[n] = vals[n].ConvertToInt();
+                        }
+                }
+                // ---- EvalFastKeySwitchCoreExt, :454-476 (the key towers are already those of QlP) ----
+                DCRTPoly cTilda0(paramsQlP, Format::EVALUATION, true), cTilda1(paramsQlP, Format::EVALUATION, true);
+                for (uint32_t j = 0; j < numPartQl; j++)
+                    for (uint32_t i = 0; i < T; i++) {
+                        const auto& cji = partsCtExt[j].GetElementAtIndex(i);
+                        cTilda0.SetElementAtIndex(i, cTilda0.GetElementAtIndex(i) + cji * bv[j].GetElementAtIndex(i));
+                        cTilda1.SetElementAtIndex(i, cTilda1.GetElementAtIndex(i) + cji * av[j].GetElementAtIndex(i));
+                    }
+                // ---- EvalFastKeySwitchCore, :430-440 ----
+                out[0]->v.push_back(cTilda0.ApproxModDown(Ql->params, paramsP, PInv, PInvPrecon, tb.hatInv, tb.hatInvPrecon, tb.hatModp,
+                                                          tb.mu, tInv, tInvPrecon, NativeInteger(t), tModqPrecon));
+                out[1]->v.push_back(cTilda1.ApproxModDown(Ql->params, paramsP, PInv, PInvPrecon, tb.hatInv, tb.hatInvPrecon, tb.hatModp,
+                                                          tb.mu, tInv, tInvPrecon, NativeInteger(t), tModqPrecon));
+                bi++;
+            }
+        }
+        catch (const std::exception& e) { err = e.what(); rc = 1; }
+    });
+    if (rc) g_ref_err = err;
+    return rc;
+}
+
 int ref_max_threads(void) { return omp_get_max_threads(); }
 // Thread count for the reference's own `omp parallel for` regions (the batch loops above pass theirs explicitly).
 // OpenFHE caps its tower loops at the value omp_get_max_threads() had when the library was loaded

@@ -60,6 +60,10 @@ class Oracle:
             ("orc_expand_ql_hat", None, [vp, vp, sz, u32, vp, u32, u32, vp]),
             ("orc_scale_round_p_over_q", None, [vp, vp, sz, u32, vp, u32, vp]),
             ("orc_uniform_at", u64, [u64, u64, u64]), ("orc_fill_uniform", None, [vp, sz, u64, u64, u64]),
+            ("orc_keyswitch_digits", u32, [u32, u32]),
+            ("orc_keyswitch_precompute", None, [vp, u32, u32, vp, vp, sz]),
+            ("orc_keyswitch_inner", None, [vp, u32, vp, vp, vp, vp, vp, sz]),
+            ("orc_keyswitch_hybrid", None, [vp, u32, u32, vp, vp, vp, vp, vp, sz, u64]),
         ]:
             f = getattr(L, name)
             f.restype, f.argtypes = res, args
@@ -111,6 +115,29 @@ class Oracle:
 
     def ctx(self, n, q, psi):
         return OracleCtx(self, n, q, psi)
+
+    # hybrid key switching (keyswitch-hybrid.cpp:324-480): qlp = OracleCtx over the sizeQl towers of Ql followed by P
+    def keyswitch_precompute(self, qlp, size_ql, alpha, c):
+        c = np.ascontiguousarray(c, np.uint64)
+        B, T, n = c.shape[0], len(qlp.q), qlp.n
+        digits = np.empty((self.L.orc_keyswitch_digits(size_ql, alpha), B, T, n), np.uint64)
+        self.L.orc_keyswitch_precompute(qlp.h, size_ql, alpha, _p(digits), _p(c), B)
+        return digits
+
+    def keyswitch_inner(self, qlp, digits, evk_b, evk_a):
+        digits = np.ascontiguousarray(digits, np.uint64)
+        c0, c1 = np.empty(digits.shape[1:], np.uint64), np.empty(digits.shape[1:], np.uint64)
+        self.L.orc_keyswitch_inner(qlp.h, digits.shape[0], _p(c0), _p(c1), _p(digits), _p(np.ascontiguousarray(evk_b, np.uint64)),
+                                   _p(np.ascontiguousarray(evk_a, np.uint64)), digits.shape[1])
+        return c0, c1
+
+    def keyswitch_hybrid(self, qlp, size_ql, alpha, c, evk_b, evk_a, t=0):
+        c = np.ascontiguousarray(c, np.uint64)
+        B, n = c.shape[0], qlp.n
+        ct0, ct1 = np.empty((B, size_ql, n), np.uint64), np.empty((B, size_ql, n), np.uint64)
+        self.L.orc_keyswitch_hybrid(qlp.h, size_ql, alpha, _p(ct0), _p(ct1), _p(c), _p(np.ascontiguousarray(evk_b, np.uint64)),
+                                    _p(np.ascontiguousarray(evk_a, np.uint64)), B, int(t))
+        return ct0, ct1
 
     def fill_uniform(self, n, q, seed, first=0):
         x = np.empty(n, np.uint64)

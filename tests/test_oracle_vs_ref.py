@@ -386,3 +386,35 @@ def test_times_tower_constants_matches_reference(oracle, ref):
     ref.ref_polys_store(hr, p(res))
     assert np.array_equal(res, oracle.expand_ql_hat(x, n, q, towers, k))
     ref.ref_polys_free(hr); ref.ref_polys_free(hx); ref.ref_ctx_destroy(c)
+
+
+@pytest.mark.parametrize("n,size_ql,size_p,alpha,t,nbits", [
+    (64, 6, 2, 2, 0, 60), (64, 5, 2, 2, 0, 60), (128, 4, 3, 3, 0, 45), (64, 7, 3, 3, 65537, 55), (32, 3, 1, 1, 0, 30),
+])
+def test_hybrid_key_switching_matches_reference(oracle, ref, n, size_ql, size_p, alpha, t, nbits):
+    """orc_keyswitch_* against the statements of KeySwitchHYBRID (keyswitch-hybrid.cpp:330-480) run on the reference's own
+    DCRTPoly: digits (incl. a shorter last digit), the inner product with the key, both ApproxModDown (CKKS and BGV form)."""
+    ref.ref_keyswitch_hybrid.argtypes = [vp, vp, u32, u32, vp, vp, u64, ctypes.POINTER(vp), vp]
+    T, B = size_ql + size_p, 2
+    q, psi = oracle.gen_params(nbits, n, T)
+    cQl = ref.ref_ctx_create(n, size_ql, p(q[:size_ql].copy()), p(psi[:size_ql].copy()))
+    cQlP = ref.ref_ctx_create(n, T, p(q), p(psi))
+    qlp = oracle.ctx(n, q, psi)
+    np_ = (size_ql + alpha - 1) // alpha
+    c = oracle.fill_ring(B, n, q[:size_ql].copy(), 91)
+    c[0, :, 0] = q[:size_ql] - 1
+    evk_b = oracle.fill_ring(np_, n, q, 92)
+    evk_a = oracle.fill_ring(np_, n, q, 93)
+    hc = ref.ref_polys_load(cQl, p(c), B, 0)
+    outs = (vp * 2)()
+    digits = np.empty((np_, B, T, n), np.uint64)
+    assert ref.ref_keyswitch_hybrid(hc, cQlP, size_ql, alpha, p(evk_b), p(evk_a), t, outs, p(digits)) == 0, ref.ref_last_error()
+    assert np.array_equal(oracle.keyswitch_precompute(qlp, size_ql, alpha, c), digits), "digits"
+    want = oracle.keyswitch_hybrid(qlp, size_ql, alpha, c, evk_b, evk_a, t)
+    for k in range(2):
+        res = np.empty((B, size_ql, n), np.uint64)
+        ref.ref_polys_store(outs[k], p(res))
+        assert np.array_equal(res, want[k]), f"ct{k}"
+        ref.ref_polys_free(outs[k])
+    ref.ref_polys_free(hc)
+    ref.ref_ctx_destroy(cQl); ref.ref_ctx_destroy(cQlP)

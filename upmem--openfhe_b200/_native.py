@@ -94,6 +94,12 @@ SIGNATURES = {
     "fhe_dcrt_chain_host": (ci, [vp, ctypes.POINTER(ci), ci, vp, vp, sz]),
     "fhe_ntt_host": (ci, [vp, vp, sz, ci]),
     "fhe_imad_probe": (ci, [vp, ci, ci, ci, ctypes.POINTER(ctypes.c_float)]),
+    "fhe_keyswitch_create": (ci, [vp, u32, u32, ctypes.POINTER(vp)]),
+    "fhe_keyswitch_destroy": (ci, [vp]),
+    "fhe_keyswitch_digits": (u32, [vp]),
+    "fhe_keyswitch_precompute": (ci, [vp, u64, u64, sz, ci]),
+    "fhe_keyswitch_inner": (ci, [vp, u64, u64, u64, u64, u64, sz, ci]),
+    "fhe_keyswitch_hybrid": (ci, [vp, u64, u64, u64, u64, u64, sz, u64, ci]),
     "fhe_group_create": (ci, [ci, vp, ctypes.c_char_p, ctypes.POINTER(vp)]),
     "fhe_group_destroy": (ci, [vp]),
     "fhe_group_size": (ci, [vp]),

@@ -1791,6 +1791,149 @@ extern "C" int fhe_imad_probe(fhe_ctx* ctx, int blocks, int threads, int iters, 
 }
 
 // ---------------------------------------------------------------------------------------------
+// hybrid key switching as one device composition (KeySwitchHYBRID, src/pke/lib/keyswitch/keyswitch-hybrid.cpp:324-480)
+// ---------------------------------------------------------------------------------------------
+struct fhe_keyswitch {
+    fhe_ctx* ctx = nullptr;
+    fhe_ring* qlp = nullptr;                      // caller's ring over the towers of Ql followed by P
+    uint32_t size_ql = 0, size_p = 0, alpha = 0;
+    fhe_ring *ql = nullptr, *p = nullptr;         // views
+    struct Part {
+        uint32_t s = 0, e = 0;                    // the digit's towers [s, e)
+        fhe_ring *part = nullptr, *lo = nullptr, *hi = nullptr;       // views: the digit, the towers below it, the towers above it (incl. P)
+        fhe_basis *to_lo = nullptr, *to_hi = nullptr;                 // ApproxSwitchCRTBasis digit -> complement, in two contiguous pieces
+    };
+    std::vector<Part> parts;
+    fhe_basis* p_to_ql = nullptr;                 // ApproxModDown
+    Scratch coef, digits, c0, c1;
+};
+
+extern "C" int fhe_keyswitch_destroy(fhe_keyswitch* k) {
+    if (!k) return FHE_OK;
+    cudaSetDevice(k->ctx->device);
+    cudaDeviceSynchronize();
+    for (auto& pt : k->parts) {
+        fhe_basis_destroy(pt.to_lo); fhe_basis_destroy(pt.to_hi);
+        fhe_ring_destroy(pt.part); fhe_ring_destroy(pt.lo); fhe_ring_destroy(pt.hi);
+    }
+    fhe_basis_destroy(k->p_to_ql);
+    fhe_ring_destroy(k->ql); fhe_ring_destroy(k->p);
+    k->coef.drop(k->ctx); k->digits.drop(k->ctx); k->c0.drop(k->ctx); k->c1.drop(k->ctx);
+    delete k;
+    return FHE_OK;
+}
+
+extern "C" int fhe_keyswitch_create(fhe_ring* ring_qlp, uint32_t size_ql, uint32_t alpha, fhe_keyswitch** out) {
+    if (!ring_qlp || !out) return fail(FHE_EINVAL, "fhe_keyswitch_create: null argument");
+    *out = nullptr;
+    const uint32_t T = ring_qlp->dev.T;
+    if (size_ql == 0 || size_ql >= T) return fail(FHE_EINVAL, "fhe_keyswitch_create: size_ql=%u must leave at least one tower of P in the ring's %u", size_ql, T);
+    if (alpha == 0) return fail(FHE_EINVAL, "fhe_keyswitch_create: alpha (towers per digit) is zero");
+    if (ring_qlp->dev.N < 2) return fail(FHE_EUNSUPPORTED, "fhe_keyswitch_create: N must be at least 2");
+    auto* k = new fhe_keyswitch;
+    k->ctx = ring_qlp->ctx; k->qlp = ring_qlp; k->size_ql = size_ql; k->size_p = T - size_ql; k->alpha = alpha;
+    int rc;
+    if ((rc = fhe_ring_view(ring_qlp, 0, size_ql, &k->ql)) || (rc = fhe_ring_view(ring_qlp, size_ql, T - size_ql, &k->p)) ||
+        (rc = fhe_basis_create(k->p, k->ql, nullptr, nullptr, &k->p_to_ql))) {
+        fhe_keyswitch_destroy(k);
+        return rc;
+    }
+    for (uint32_t s = 0; s < size_ql; s += alpha) {
+        fhe_keyswitch::Part pt;
+        pt.s = s; pt.e = std::min(s + alpha, size_ql);
+        k->parts.push_back(pt);
+        auto& P = k->parts.back();
+        // the digit's own tables, products over its (possibly truncated) basis: rns-cryptoparameters.cpp:289-340
+        if ((rc = fhe_ring_view(ring_qlp, P.s, P.e - P.s, &P.part)) ||
+            (P.s > 0 && ((rc = fhe_ring_view(ring_qlp, 0, P.s, &P.lo)) || (rc = fhe_basis_create(P.part, P.lo, nullptr, nullptr, &P.to_lo)))) ||
+            (rc = fhe_ring_view(ring_qlp, P.e, T - P.e, &P.hi)) || (rc = fhe_basis_create(P.part, P.hi, nullptr, nullptr, &P.to_hi))) {
+            fhe_keyswitch_destroy(k);
+            return rc;
+        }
+    }
+    *out = k;
+    return FHE_OK;
+}
+
+extern "C" uint32_t fhe_keyswitch_digits(const fhe_keyswitch* k) { return k ? (uint32_t)k->parts.size() : 0; }
+
+// EvalKeySwitchPrecomputeCore (keyswitch-hybrid.cpp:330-420) on stream s: digits [np][batch][T][N]
+static int keyswitch_precompute(fhe_keyswitch* k, uint64_t* digits, const uint64_t* c, size_t batch, cudaStream_t s) {
+    const uint32_t N = k->qlp->dev.N, logN = k->qlp->dev.logN, T = k->qlp->dev.T;
+    const char* who = "fhe_keyswitch_precompute";
+    int rc;
+    if ((rc = k->coef.need(k->ctx, batch * std::min(k->alpha, k->size_ql) * (size_t)N * 8))) return rc;
+    uint64_t* coef = (uint64_t*)k->coef.p;
+    for (size_t j = 0; j < k->parts.size(); j++) {
+        auto& P = k->parts[j];
+        const uint32_t sp = P.e - P.s;
+        uint64_t* d = digits + j * batch * (size_t)T * N;
+        // the digit's towers, COEFFICIENT (:392-393): read where they lie in c, packed into the scratch
+        if ((rc = ring_ntt(P.part, coef, batch, true, s, who, c + (size_t)P.s * N, sp, k->size_ql))) return rc;
+        // ApproxSwitchCRTBasis to the complement basis (:396-402), written where the towers belong in the digit, then
+        // EVALUATION (:404) in place there
+        if (P.lo) {
+            CUDA_TRY(launch_basis_switch(P.to_lo->dev, d, T, 0, coef, sp, 0, batch, logN, false, s));
+            if ((rc = ring_ntt(P.lo, d, batch, false, s, who, nullptr, T))) return rc;
+        }
+        CUDA_TRY(launch_basis_switch(P.to_hi->dev, d, T, P.e, coef, sp, 0, batch, logN, false, s));
+        if ((rc = ring_ntt(P.hi, d + (size_t)P.e * N, batch, false, s, who, nullptr, T))) return rc;
+        CUDA_TRY(copy_towers(d, T, P.s, c, k->size_ql, P.s, sp, batch, N, s));      // the digit's own stored towers (:410-412)
+    }
+    return FHE_OK;
+}
+
+extern "C" int fhe_keyswitch_precompute(fhe_keyswitch* k, fhe_dptr digits, fhe_dptr c, size_t batch, int stream) {
+    if (!k) return fail(FHE_EINVAL, "null key-switching plan");
+    StreamRef s;
+    int rc = ring_stream(k->qlp, stream, &s);
+    if (rc) return rc;
+    if (batch == 0) return FHE_OK;
+    if (!digits || !c) return fail(FHE_EINVAL, "fhe_keyswitch_precompute: null device pointer");
+    if ((digits | c) & 15) return fail(FHE_EINVAL, "fhe_keyswitch_precompute: device pointers must be 16-byte aligned");
+    return keyswitch_precompute(k, (uint64_t*)(uintptr_t)digits, (const uint64_t*)(uintptr_t)c, batch, s);
+}
+
+extern "C" int fhe_keyswitch_inner(fhe_keyswitch* k, fhe_dptr ctilda0, fhe_dptr ctilda1, fhe_dptr digits, fhe_dptr evk_b,
+                                   fhe_dptr evk_a, size_t batch, int stream) {
+    if (!k) return fail(FHE_EINVAL, "null key-switching plan");
+    StreamRef s;
+    int rc = ring_stream(k->qlp, stream, &s);
+    if (rc) return rc;
+    if (batch == 0) return FHE_OK;
+    if (!ctilda0 || !ctilda1 || !digits || !evk_b || !evk_a) return fail(FHE_EINVAL, "fhe_keyswitch_inner: null device pointer");
+    if (ctilda0 == ctilda1) return fail(FHE_EINVAL, "fhe_keyswitch_inner: the two outputs must be distinct");
+    if ((ctilda0 | ctilda1 | digits | evk_b | evk_a) & 15) return fail(FHE_EINVAL, "fhe_keyswitch_inner: device pointers must be 16-byte aligned");
+    CUDA_TRY(launch_ks_inner(k->qlp->dev, (uint64_t*)(uintptr_t)ctilda0, (uint64_t*)(uintptr_t)ctilda1, (const uint64_t*)(uintptr_t)digits,
+                             (const uint64_t*)(uintptr_t)evk_b, (const uint64_t*)(uintptr_t)evk_a, (uint32_t)k->parts.size(), batch, s));
+    return FHE_OK;
+}
+
+extern "C" int fhe_keyswitch_hybrid(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1, fhe_dptr c, fhe_dptr evk_b, fhe_dptr evk_a,
+                                    size_t batch, uint64_t t, int stream) {
+    if (!k) return fail(FHE_EINVAL, "null key-switching plan");
+    if (batch == 0) return FHE_OK;
+    if (!ct0 || !ct1 || !c || !evk_b || !evk_a) return fail(FHE_EINVAL, "fhe_keyswitch_hybrid: null device pointer");
+    if (ct0 == ct1) return fail(FHE_EINVAL, "fhe_keyswitch_hybrid: the two outputs must be distinct");
+    if ((ct0 | ct1 | c | evk_b | evk_a) & 15) return fail(FHE_EINVAL, "fhe_keyswitch_hybrid: device pointers must be 16-byte aligned");
+    const size_t item = (size_t)k->qlp->dev.T * k->qlp->dev.N * 8;
+    int rc;
+    if ((rc = k->digits.need(k->ctx, k->parts.size() * batch * item)) || (rc = k->c0.need(k->ctx, batch * item)) ||
+        (rc = k->c1.need(k->ctx, batch * item)))
+        return rc;
+    {
+        StreamRef s;
+        if ((rc = ring_stream(k->qlp, stream, &s))) return rc;
+        if ((rc = keyswitch_precompute(k, (uint64_t*)k->digits.p, (const uint64_t*)(uintptr_t)c, batch, s))) return rc;
+        CUDA_TRY(launch_ks_inner(k->qlp->dev, (uint64_t*)k->c0.p, (uint64_t*)k->c1.p, (const uint64_t*)k->digits.p,
+                                 (const uint64_t*)(uintptr_t)evk_b, (const uint64_t*)(uintptr_t)evk_a, (uint32_t)k->parts.size(), batch, s));
+    }
+    // EvalFastKeySwitchCore (:430-440): both halves back to Ql
+    if ((rc = fhe_approx_mod_down(k->p_to_ql, ct0, (fhe_dptr)(uintptr_t)k->c0.p, batch, t, stream))) return rc;
+    return fhe_approx_mod_down(k->p_to_ql, ct1, (fhe_dptr)(uintptr_t)k->c1.p, batch, t, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
 // several devices of one node: the batch is split in contiguous blocks, one per device, every
 // device holds the ring's tables, no collective runs inside the path.  NCCL (loaded at run time: libnccl.so.2)
 // carries only the optional gather of results over NVLink / NVSwitch, on the library's own streams.

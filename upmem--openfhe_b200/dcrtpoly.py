@@ -730,3 +730,32 @@ class Comm:
         if self.h:
             N.lib.fhe_comm_destroy(self.h)
             self.h = None
+
+
+class KeySwitch:
+    """Hybrid key switching at one level (KeySwitchHYBRID, keyswitch-hybrid.cpp:324-480) as a device composition.
+    `ring_qlp`: the size_ql current towers of Q followed by P; alpha: towers per digit."""
+
+    def __init__(self, ring_qlp, size_ql, alpha):
+        self.ring, self.size_ql, self.alpha = ring_qlp, int(size_ql), int(alpha)
+        h = ctypes.c_void_p()
+        N.check(N.lib.fhe_keyswitch_create(ring_qlp.h, self.size_ql, self.alpha, ctypes.byref(h)))
+        self.h = h
+        self.digits = N.lib.fhe_keyswitch_digits(h)
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_keyswitch_destroy(self.h)
+            self.h = None
+
+    def precompute(self, digits, c, batch, stream=0):
+        """EvalKeySwitchPrecomputeCore: c over Ql (EVALUATION) -> digits [digits][batch][T][N]."""
+        N.check(N.lib.fhe_keyswitch_precompute(self.h, digits, c, batch, stream))
+
+    def inner(self, ctilda0, ctilda1, digits, evk_b, evk_a, batch, stream=0):
+        """EvalFastKeySwitchCoreExt: the inner product with the key (given over the towers of ring_qlp)."""
+        N.check(N.lib.fhe_keyswitch_inner(self.h, ctilda0, ctilda1, digits, evk_b, evk_a, batch, stream))
+
+    def __call__(self, ct0, ct1, c, evk_b, evk_a, batch, t=0, stream=0):
+        """KeySwitchCore: ct0, ct1 over Ql."""
+        N.check(N.lib.fhe_keyswitch_hybrid(self.h, ct0, ct1, c, evk_b, evk_a, batch, int(t), stream))
