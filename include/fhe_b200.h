@@ -265,6 +265,23 @@ int fhe_drop_last_element_and_scale(fhe_rescale* plan, fhe_dptr dst, fhe_dptr sr
  * [-t^-1]_{ql} and [t]_{q_i} (bgvrns-cryptoparameters.cpp:91-99) are derived here.  Format is preserved. */
 int fhe_mod_reduce(fhe_rescale* plan, fhe_dptr dst, fhe_dptr src, size_t batch, uint64_t t, int format, int stream);
 
+/* ---- BFV decryption: the scaling step ------------------------------------------------------------ */
+/* DCRTPolyImpl::ScaleAndRound(t, tQHatInvModqDivqModt, ..Precon, tQHatInvModqBDivqModt, ..Precon, tQHatInvModqDivqFrac,
+ * tQHatInvModqBDivqFrac) -> NativePoly (dcrtpoly-impl.h:1537-1816): src over the ring Q [batch][T][N], COEFFICIENT ->
+ * dst [batch][N] = round(t/Q * x) mod t.  The reference picks one of eight branches from the bit lengths of q_0, t and
+ * the tower count (t a power of two; residues used whole or split in halves; products reduced modulo t or not); the
+ * same choice is made here and every branch follows the reference statement for statement, IEEE doubles in its order
+ * of operations.  Tables: the scheme's (bfvrns-cryptoparameters.cpp:447-494: modt / frac, and b_modt / b_frac for the
+ * split branch), or NULL to have them derived from the moduli; Shoup companions are built here.  2 <= t < 2^60. */
+typedef struct fhe_decrypt_scale fhe_decrypt_scale;
+int fhe_decrypt_scale_create(fhe_ring* ring, uint64_t t, const uint64_t* modt, const uint64_t* b_modt, const double* frac,
+                             const double* b_frac, fhe_decrypt_scale** out);
+int fhe_decrypt_scale_destroy(fhe_decrypt_scale* plan);
+/* host copies of the tables in use; *branch = 4 * (t power of two) + 2 * (split) + (products reduced modulo t) */
+int fhe_decrypt_scale_tables(const fhe_decrypt_scale* plan, uint64_t* modt, uint64_t* b_modt, double* frac, double* b_frac,
+                             int* branch);
+int fhe_scale_and_round_native(fhe_decrypt_scale* plan, fhe_dptr dst, fhe_dptr src, size_t batch, int stream);
+
 /* ---- hybrid key switching (CKKS / BGV relinearisation and rotations) --------------------------- */
 /* KeySwitchHYBRID (src/pke/lib/keyswitch/keyswitch-hybrid.cpp:324-480) at one level as a device composition.
  * ring_qlp: the size_ql current towers of Q followed by the towers of P; alpha: towers per digit

@@ -821,6 +821,83 @@ void orc_scale_and_round(uint64_t* out, const uint64_t* in, size_t B, uint32_t N
     free(mu);
 }
 
+/* ---- BFV decryption: DCRTPolyImpl::ScaleAndRound(t, ...) -> NativePoly (dcrtpoly-impl.h:1537-1816) --------------------
+ * Tables as bfvrns-cryptoparameters.cpp:447-494 builds them (here with 128-bit integers: [(Q/q_i)^-1]_{q_i} * t < 2^124):
+ *   X_i = [(Q/q_i)^-1]_{q_i} * t;  modt = floor(X_i/q_i) mod t;  frac = double(X_i mod q_i) / double(q_i);
+ *   and, when qMSB + sizeQMSB >= 52, the same for X_i << (qMSB/2): bmodt, bfrac.
+ * branch = 4 * (t power of two) + 2 * (split) + (products reduced modulo t), chosen exactly as :1546-1631 choose. */
+int orc_decrypt_branch(const uint64_t* q, uint32_t T, uint64_t t) {
+    uint32_t qMSB = orc_msb(q[0]), tMSB = orc_msb(t), sMSB = orc_msb(T);
+    int pow2 = (t & (t - 1)) == 0, split = !(qMSB + sMSB < 52);
+    uint32_t width = (split ? (qMSB >> 1) : qMSB) + tMSB + sMSB;
+    int reduce = pow2 ? !(width < (split ? 62u : 63u)) : !(width < 52u);
+    return pow2 * 4 + split * 2 + reduce;
+}
+
+void orc_decrypt_tables(const uint64_t* q, uint32_t T, uint64_t t, uint64_t* modt, uint64_t* bmodt, double* frac, double* bfrac) {
+    uint32_t h = orc_msb(q[0]) >> 1;
+    int split = (orc_decrypt_branch(q, T, t) >> 1) & 1;
+    for (uint32_t i = 0; i < T; i++) {
+        uint64_t qi = q[i], hat = 1 % qi;
+        for (uint32_t k = 0; k < T; k++) if (k != i) hat = mulmod_u128(hat, q[k] % qi, qi);
+        u128 X = (u128)orc_modinv(hat, qi) * t, D = X / qi;
+        uint64_t R = (uint64_t)(X % qi);
+        modt[i] = (uint64_t)(D % t);
+        frac[i] = (double)(int64_t)R / (double)(int64_t)qi;
+        bmodt[i] = 0; bfrac[i] = 0.0;
+        if (split) {
+            u128 RB = (u128)R << h;
+            uint64_t two_h = (uint64_t)(((u128)1 << h) % t);
+            bmodt[i] = (uint64_t)(((u128)(uint64_t)(D % t) * two_h + (RB / qi) % t) % t);
+            bfrac[i] = (double)(int64_t)(uint64_t)(RB % qi) / (double)(int64_t)qi;
+        }
+    }
+}
+
+void orc_scale_and_round_native(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, const uint64_t* q, uint32_t T, uint64_t t,
+                                const uint64_t* modt, const uint64_t* bmodt, const double* frac, const double* bfrac) {
+    const int br = orc_decrypt_branch(q, T, t), pow2 = br >> 2, split = (br >> 1) & 1, reduce = br & 1;
+    const uint32_t h = orc_msb(q[0]) >> 1;
+    uint64_t pre[256], bpre[256];
+    for (uint32_t i = 0; i < T; i++) { pre[i] = orc_prep_mulconst(modt[i], t); bpre[i] = orc_prep_mulconst(bmodt[i], t); }
+    const double td = (double)t, tInv = 1. / td;
+    long items = (long)(B * N);
+#pragma omp parallel for schedule(static)
+    for (long e = 0; e < items; e++) {
+        size_t b = (size_t)e / N, ri = (size_t)e % N;
+        volatile double floatSum = pow2 ? 0.5 : 0.0;          /* volatile: every product and sum is rounded to double */
+        uint64_t intSum = 0;
+        for (uint32_t i = 0; i < T; i++) {
+            uint64_t tmp = in[(b * T + i) * N + ri];
+            if (!split) {
+                volatile double prod = (double)tmp * frac[i];
+                floatSum = floatSum + prod;
+                intSum += reduce ? orc_modmul_const(tmp, modt[i], t, pre[i]) : tmp * modt[i];
+            } else {
+                uint64_t hi = tmp >> h, lo = tmp - (hi << h);
+                volatile double p1 = (double)lo * frac[i];
+                floatSum = floatSum + p1;
+                volatile double p2 = (double)hi * bfrac[i];
+                floatSum = floatSum + p2;
+                intSum += reduce ? orc_modmul_const(lo, modt[i], t, pre[i]) : lo * modt[i];
+                intSum += reduce ? orc_modmul_const(hi, bmodt[i], t, bpre[i]) : hi * bmodt[i];
+            }
+        }
+        if (pow2) {
+            intSum += (uint64_t)floatSum;
+            out[e] = intSum & (t - 1);
+        } else {
+            floatSum = floatSum + (double)intSum;
+            volatile double qd = floatSum * tInv;
+            uint64_t quot = (uint64_t)qd;
+            volatile double sub = td * (double)quot;
+            floatSum = floatSum - sub;
+            volatile double rr = floatSum + 0.5;
+            out[e] = (uint64_t)rr;
+        }
+    }
+}
+
 /* ---- hybrid key switching (KeySwitchHYBRID, src/pke/lib/keyswitch/keyswitch-hybrid.cpp) ----------------------------
  * QlP = the ring over the sizeQl current towers of Q followed by the sizeP towers of P.  Digits of alpha towers
  * (the last may be shorter), numPart = ceil(sizeQl / alpha)  (:345-348, without the cap at GetNumberOfQPartitions:

@@ -77,6 +77,11 @@ void     orc_ctx_destroy(orc_ctx* c);
 void     orc_dcrt_elementwise(const orc_ctx* c, int op, uint64_t* dst, const uint64_t* a,
                               const uint64_t* b, size_t B, int nthreads);
 void     orc_dcrt_ntt(const orc_ctx* c, int inverse, uint64_t* x, size_t B, int nthreads);
+/* BFV decryption: ScaleAndRound(t, ...) -> NativePoly (dcrtpoly-impl.h:1537-1816); tables of bfvrns-cryptoparameters.cpp:447-494 */
+int      orc_decrypt_branch(const uint64_t* q, uint32_t T, uint64_t t);
+void     orc_decrypt_tables(const uint64_t* q, uint32_t T, uint64_t t, uint64_t* modt, uint64_t* bmodt, double* frac, double* bfrac);
+void     orc_scale_and_round_native(uint64_t* out, const uint64_t* in, size_t B, uint32_t N, const uint64_t* q, uint32_t T, uint64_t t,
+                                    const uint64_t* modt, const uint64_t* bmodt, const double* frac, const double* bfrac);
 /* hybrid key switching (keyswitch-hybrid.cpp:324-480); QlP = sizeQl towers of Q then P; digits of alpha towers */
 uint32_t orc_keyswitch_digits(uint32_t sizeQl, uint32_t alpha);
 void     orc_keyswitch_precompute(const orc_ctx* QlP, uint32_t sizeQl, uint32_t alpha, uint64_t* digits, const uint64_t* c, size_t B);

@@ -866,6 +866,62 @@ ref_polys* ref_polys_deserialize(ref_ctx* c, const uint8_t* bytes, size_t len) {
     }
 }
 
+// ---- BFV decryption: DCRTPoly::ScaleAndRound(t, ...) -> NativePoly (dcrtpoly-impl.h:1537-1816) ------------------------
+// Tables built with the reference's BigInteger exactly as bfvrns-cryptoparameters.cpp:447-494 builds them.
+// out [B][N]; the tables come back for comparison with the restated ones (bmodt / bfrac are zero when the split
+// branch is not taken).
+int ref_polys_scale_and_round_native(const ref_polys* a, uint64_t t, uint64_t* out, uint64_t* modt_out, uint64_t* bmodt_out,
+                                     double* frac_out, double* bfrac_out) {
+    int rc = 0;
+    std::string err;
+    serial_omp([&] {
+        try {
+            ref_ctx* Q   = a->ctx;
+            auto moduliQ = moduli_of(Q);
+            size_t sizeQ = moduliQ.size();
+            BigInteger modulusQ(1);
+            for (auto& qi : moduliQ) modulusQ *= BigInteger(qi);
+            const BigInteger T(t);
+            usint qMSB = moduliQ[0].GetMSB(), sizeQMSB = GetMSB64(sizeQ);
+            std::vector<NativeInteger> modt(sizeQ), modtPrecon(sizeQ), bmodt, bmodtPrecon;
+            std::vector<double> frac(sizeQ), bfrac;
+            const bool split = !(qMSB + sizeQMSB < 52);
+            if (split) { bmodt.resize(sizeQ); bmodtPrecon.resize(sizeQ); bfrac.resize(sizeQ); }
+            usint qMSBHf = qMSB >> 1;
+            for (size_t i = 0; i < sizeQ; i++) {
+                BigInteger qi(moduliQ[i].ConvertToInt());
+                BigInteger tQHatInvModqi     = ((modulusQ.DividedBy(qi)).ModInverse(qi) * T);
+                BigInteger tQHatInvModqDivqi = tQHatInvModqi.DividedBy(qi);
+                modt[i]                      = tQHatInvModqDivqi.Mod(T).ConvertToInt();
+                modtPrecon[i]                = modt[i].PrepModMulConst(NativeInteger(t));
+                int64_t numerator            = tQHatInvModqi.Mod(qi).ConvertToInt();
+                int64_t denominator          = moduliQ[i].ConvertToInt();
+                frac[i]                      = static_cast<double>(numerator) / static_cast<double>(denominator);
+                if (split) {
+                    tQHatInvModqi.LShiftEq(qMSBHf);
+                    tQHatInvModqDivqi = tQHatInvModqi.DividedBy(qi);
+                    bmodt[i]          = tQHatInvModqDivqi.Mod(T).ConvertToInt();
+                    bmodtPrecon[i]    = bmodt[i].PrepModMulConst(NativeInteger(t));
+                    numerator         = tQHatInvModqi.Mod(qi).ConvertToInt();
+                    bfrac[i]          = static_cast<double>(numerator) / static_cast<double>(denominator);
+                }
+                modt_out[i] = modt[i].ConvertToInt(); frac_out[i] = frac[i];
+                bmodt_out[i] = split ? bmodt[i].ConvertToInt() : 0; bfrac_out[i] = split ? bfrac[i] : 0.0;
+            }
+            size_t b = 0;
+            for (auto& poly : a->v) {
+                NativePoly r = poly.ScaleAndRound(NativeInteger(t), modt, modtPrecon, bmodt, bmodtPrecon, frac, bfrac);
+                const auto& vals = r.GetValues();
+                for (uint32_t j = 0; j < Q->N; j++) out[b * Q->N + j] = vals[j].ConvertToInt();
+                b++;
+            }
+        }
+        catch (const std::exception& e) { err = e.what(); rc = 1; }
+    });
+    if (rc) g_ref_err = err;
+    return rc;
+}
+
 // ---- hybrid key switching on the reference's own DCRTPoly -----------------------------------------------------------
 // The statements of KeySwitchHYBRID::EvalKeySwitchPrecomputeCore / EvalFastKeySwitchCoreExt / EvalFastKeySwitchCore
 // (src/pke/lib/keyswitch/keyswitch-hybrid.cpp:330-480) — src/pke itself is not compiled here — with the tables the

@@ -60,6 +60,9 @@ class Oracle:
             ("orc_expand_ql_hat", None, [vp, vp, sz, u32, vp, u32, u32, vp]),
             ("orc_scale_round_p_over_q", None, [vp, vp, sz, u32, vp, u32, vp]),
             ("orc_uniform_at", u64, [u64, u64, u64]), ("orc_fill_uniform", None, [vp, sz, u64, u64, u64]),
+            ("orc_decrypt_branch", ci, [vp, u32, u64]),
+            ("orc_decrypt_tables", None, [vp, u32, u64, vp, vp, vp, vp]),
+            ("orc_scale_and_round_native", None, [vp, vp, sz, u32, vp, u32, u64, vp, vp, vp, vp]),
             ("orc_keyswitch_digits", u32, [u32, u32]),
             ("orc_keyswitch_precompute", None, [vp, u32, u32, vp, vp, sz]),
             ("orc_keyswitch_inner", None, [vp, u32, vp, vp, vp, vp, vp, sz]),
@@ -115,6 +118,24 @@ class Oracle:
 
     def ctx(self, n, q, psi):
         return OracleCtx(self, n, q, psi)
+
+    # BFV decryption: ScaleAndRound(t, ...) -> NativePoly (dcrtpoly-impl.h:1537-1816)
+    def decrypt_tables(self, q, t):
+        q = np.ascontiguousarray(q, np.uint64)
+        T = len(q)
+        modt, bmodt = np.zeros(T, np.uint64), np.zeros(T, np.uint64)
+        frac, bfrac = np.zeros(T, np.float64), np.zeros(T, np.float64)
+        self.L.orc_decrypt_tables(_p(q), T, int(t), _p(modt), _p(bmodt), _p(frac), _p(bfrac))
+        return modt, bmodt, frac, bfrac, self.L.orc_decrypt_branch(_p(q), T, int(t))
+
+    def scale_and_round_native(self, x, n, q, t, tables=None):
+        q = np.ascontiguousarray(q, np.uint64)
+        x = np.ascontiguousarray(x, np.uint64)
+        modt, bmodt, frac, bfrac = (tables or self.decrypt_tables(q, t))[:4]
+        B = x.size // (len(q) * n)
+        out = np.empty((B, n), np.uint64)
+        self.L.orc_scale_and_round_native(_p(out), _p(x), B, n, _p(q), len(q), int(t), _p(modt), _p(bmodt), _p(frac), _p(bfrac))
+        return out
 
     # hybrid key switching (keyswitch-hybrid.cpp:324-480): qlp = OracleCtx over the sizeQl towers of Ql followed by P
     def keyswitch_precompute(self, qlp, size_ql, alpha, c):

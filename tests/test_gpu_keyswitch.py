@@ -59,3 +59,66 @@ def test_keyswitch_argument_checks(pkg, backend, oracle):
     backend.free(x)
     ks.close()
     ring.close()
+
+
+# ---- BFV decryption: ScaleAndRound(t, ...) -> NativePoly (dcrtpoly-impl.h:1537-1816), every branch ---------------
+@pytest.mark.parametrize("nbits,towers,t,branch", [
+    (40, 4, 1 << 10, 4), (40, 4, 1 << 30, 5), (60, 4, 1 << 16, 6), (60, 4, 1 << 40, 7),
+    (30, 4, 65537, 0), (40, 4, 65537, 1), (60, 4, 65537, 2), (60, 4, 33554467, 3), (60, 40, 65537, 3), (55, 2, 2, 6),
+    (60, 16, 65537, 3), (60, 30, 1 << 20, 6),
+])
+def test_decrypt_scale_and_round_vs_oracle(pkg, backend, oracle, nbits, towers, t, branch):
+    n, batch = 1 << 11, 3
+    q, psi = oracle.gen_params(nbits, n, towers)
+    ring = pkg.Ring(backend, n, q, psi)
+    want_tables = oracle.decrypt_tables(q, t)
+    assert want_tables[4] == branch
+    plan = pkg.DecryptScale(ring, t)                         # tables derived from the moduli
+    got = plan.tables()
+    assert got[4] == branch
+    for a, b in zip(got[:2], want_tables[:2]):
+        assert np.array_equal(a, b)
+    for a, b in zip(got[2:4], want_tables[2:4]):
+        assert np.array_equal(a.view(np.uint64), b.view(np.uint64))
+    x = oracle.fill_ring(batch, n, q, 311)
+    x[0, :, 0] = q - 1
+    x[0, :, 1] = 0
+    x[1, :, 2] = q >> np.uint64(1)
+    dx, dy = backend.alloc(x.nbytes), backend.alloc(batch * n * 8)
+    backend.h2d(dx, x)
+    plan(dy, dx, batch)
+    want = oracle.scale_and_round_native(x, n, q, t)
+    assert np.array_equal(backend.d2h(dy, batch * n).reshape(batch, n), want)
+    plan2 = pkg.DecryptScale(ring, t, want_tables[:4])       # the scheme's own tables passed in
+    plan2(dy, dx, batch)
+    assert np.array_equal(backend.d2h(dy, batch * n).reshape(batch, n), want)
+    plan.close(); plan2.close()
+    backend.free(dx); backend.free(dy)
+    ring.close()
+
+
+def test_decrypt_scale_recovers_a_scaled_message(pkg, backend, oracle):
+    """Property at full size (N = 2^15, 16 towers): x = round(Q/t * m) + small noise decrypts to m."""
+    n, towers, t = 1 << 15, 16, 65537
+    q, psi = oracle.gen_params(60, n, towers)
+    Q = 1
+    for qi in q:
+        Q *= int(qi)
+    rng = np.random.default_rng(5)
+    m = rng.integers(0, t, size=n, dtype=np.uint64)
+    noise = rng.integers(-1000, 1000, size=n)
+    x = np.empty((1, towers, n), np.uint64)
+    big = [((Q * int(mi) + t // 2) // t + int(ei)) % Q for mi, ei in zip(m[:64], noise[:64])]
+    for i, qi in enumerate(q):
+        x[0, i, :64] = [b % int(qi) for b in big]
+    m[64:] = 0
+    x[0, :, 64:] = 0
+    ring = pkg.Ring(backend, n, q, psi)
+    plan = pkg.DecryptScale(ring, t)
+    dx, dy = backend.alloc(x.nbytes), backend.alloc(n * 8)
+    backend.h2d(dx, x)
+    plan(dy, dx, 1)
+    assert np.array_equal(backend.d2h(dy, n), m)
+    plan.close()
+    backend.free(dx); backend.free(dy)
+    ring.close()

@@ -418,3 +418,34 @@ def test_hybrid_key_switching_matches_reference(oracle, ref, n, size_ql, size_p,
         ref.ref_polys_free(outs[k])
     ref.ref_polys_free(hc)
     ref.ref_ctx_destroy(cQl); ref.ref_ctx_destroy(cQlP)
+
+
+# (bits of q, towers, t): one case per branch of dcrtpoly-impl.h:1537-1816, branch = 4*pow2 + 2*split + reduce
+DECRYPT_CASES = [(40, 4, 1 << 10, 4), (40, 4, 1 << 30, 5), (60, 4, 1 << 16, 6), (60, 4, 1 << 40, 7),
+                 (30, 4, 65537, 0), (40, 4, 65537, 1), (60, 4, 65537, 2), (60, 4, 33554467, 3), (60, 9, 65537, 2), (60, 40, 65537, 3), (55, 2, 2, 6)]
+
+
+@pytest.mark.parametrize("nbits,towers,t,branch", DECRYPT_CASES)
+def test_decrypt_scale_and_round_matches_reference(oracle, ref, nbits, towers, t, branch):
+    """orc_scale_and_round_native and orc_decrypt_tables against DCRTPoly::ScaleAndRound(t, ...) -> NativePoly with the
+    tables built by the reference's BigInteger as bfvrns-cryptoparameters.cpp:447-494 builds them; every branch."""
+    ref.ref_polys_scale_and_round_native.argtypes = [vp, u64, vp, vp, vp, vp, vp]
+    n, B = 256, 3
+    q, psi = oracle.gen_params(nbits, n, towers)
+    modt, bmodt, frac, bfrac, br = oracle.decrypt_tables(q, t)
+    assert br == branch
+    c = ref.ref_ctx_create(n, towers, p(q), p(psi))
+    x = oracle.fill_ring(B, n, q, 211)
+    x[0, :, 0] = q - 1
+    x[0, :, 1] = 0
+    x[1, :, 2] = q >> np.uint64(1)
+    hx = ref.ref_polys_load(c, p(x), B, 1)
+    out = np.empty((B, n), np.uint64)
+    rm, rb = np.zeros(towers, np.uint64), np.zeros(towers, np.uint64)
+    rf, rbf = np.zeros(towers, np.float64), np.zeros(towers, np.float64)
+    assert ref.ref_polys_scale_and_round_native(hx, t, p(out), p(rm), p(rb), p(rf), p(rbf)) == 0, ref.ref_last_error()
+    assert np.array_equal(rm, modt) and np.array_equal(rb, bmodt), "integer tables"
+    assert np.array_equal(rf.view(np.uint64), frac.view(np.uint64)) and np.array_equal(rbf.view(np.uint64), bfrac.view(np.uint64)), "fractions"
+    assert np.array_equal(oracle.scale_and_round_native(x, n, q, t), out)
+    assert (out < t).all()
+    ref.ref_polys_free(hx); ref.ref_ctx_destroy(c)

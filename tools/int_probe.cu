@@ -10,11 +10,14 @@ typedef unsigned long long u64;
 typedef unsigned int u32;
 constexpr int ILP = 8;
 
-enum { K_MADLO, K_MADWIDE, K_MADHI, K_MULHI64, K_MULLO64, K_SHOUP, K_SHOUP_APPROX, K_IADD3, K_MULWIDE, K_MADWIDE_IND, K_MULHI, K_BFLY, K_COUNT };
+enum { K_MADLO, K_MADWIDE, K_MADHI, K_MULHI64, K_MULLO64, K_SHOUP, K_SHOUP_APPROX, K_IADD3, K_MULWIDE, K_MADWIDE_IND, K_MULHI, K_BFLY, K_MULWIDE_BOTH, K_MADWIDE_BOTH, K_BFLY_V2, K_BFLY_V3, K_COUNT };
 static const char* names[] = {"mad.lo.u32", "mad.wide.u32", "mad.hi.u32", "__umul64hi", "mul.lo.u64 (+add)",
                               "shoup_lazy (mulhi64 + 2 mullo64)", "shoup_approx (3-product hi)", "add.u32 x3 (alu)",
                               "mul.wide.u32 (no addend)", "mad.wide.u32 (addend not from the multiplier chain)", "mul.hi.u32 (no addend)",
-                              "NTT butterfly multiplier as the kernels write it (2 mul.hi + 3 wide + 4 mad.lo)"};
+                              "NTT butterfly multiplier as the kernels write it (2 mul.hi + 3 wide + 4 mad.lo)",
+                              "mul.wide.u32, both halves of the product consumed", "mad.wide.u32 (64-bit addend), both halves consumed",
+                              "butterfly multiplier v2: 5 mul.wide (no addend) + 64-bit adds on the ALU + 4 mad.lo",
+                              "butterfly multiplier v3: 2 mul.hi + 3 mul.wide (no addend) + ALU adds + 4 mad.lo"};
 
 template <int K>
 __global__ void __launch_bounds__(256) probe(u64* out, int iters, u32 seed) {
@@ -49,6 +52,33 @@ __global__ void __launch_bounds__(256) probe(u64* out, int iters, u32 seed) {
                 u32 h0 = (u32)qh, h1 = (u32)(qh >> 32);
                 asm("mul.wide.u32 %0, %1, %2;" : "=l"(acc) : "r"(x0), "r"(w0));
                 asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(h0), "r"(n0));
+                asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(acc));
+                asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(x0), "r"(w1));
+                asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(x1), "r"(w0));
+                asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(h0), "r"(n1));
+                asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(h1), "r"(n0));
+                asm("mov.b64 %0, {%1, %2};" : "=l"(x[k]) : "r"(lo), "r"(hi));
+            }
+            if (K == K_MULWIDE_BOTH) { u64 t; asm volatile("mul.wide.u32 %0, %1, %2;" : "=l"(t) : "r"((u32)x[k]), "r"(b)); x[k] = t ^ (t >> 32); }
+            if (K == K_MADWIDE_BOTH) { u64 t = x[k]; asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(t) : "r"((u32)x[k]), "r"(b)); x[k] = t ^ (t >> 32); }
+            if (K == K_BFLY_V2 || K == K_BFLY_V3) {
+                u32 x0 = (u32)x[k], x1 = (u32)(x[k] >> 32), w0 = (u32)w, w1 = (u32)(w >> 32);
+                u32 p0 = (u32)wp, p1 = (u32)(wp >> 32), n0 = (u32)nq, n1 = (u32)(nq >> 32), t1, t2, lo, hi;
+                u64 m0, m1, m2, qh, a0, a1, acc;
+                if (K == K_BFLY_V2) {
+                    asm("mul.wide.u32 %0, %1, %2;" : "=l"(m0) : "r"(x1), "r"(p0));
+                    asm("mul.wide.u32 %0, %1, %2;" : "=l"(m1) : "r"(x0), "r"(p1));
+                    t1 = (u32)(m0 >> 32); t2 = (u32)(m1 >> 32);
+                } else {
+                    asm("mul.hi.u32 %0, %1, %2;" : "=r"(t1) : "r"(x1), "r"(p0));
+                    asm("mul.hi.u32 %0, %1, %2;" : "=r"(t2) : "r"(x0), "r"(p1));
+                }
+                asm("mul.wide.u32 %0, %1, %2;" : "=l"(m2) : "r"(x1), "r"(p1));
+                qh = m2 + (u64)t1 + (u64)t2;
+                u32 h0 = (u32)qh, h1 = (u32)(qh >> 32);
+                asm("mul.wide.u32 %0, %1, %2;" : "=l"(a0) : "r"(x0), "r"(w0));
+                asm("mul.wide.u32 %0, %1, %2;" : "=l"(a1) : "r"(h0), "r"(n0));
+                acc = a0 + a1;
                 asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(acc));
                 asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(x0), "r"(w1));
                 asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(x1), "r"(w0));
@@ -100,6 +130,10 @@ int main(int argc, char** argv) {
     run<K_MADWIDE_IND>(d, blocks, iters);
     run<K_MULHI>(d, blocks, iters);
     run<K_BFLY>(d, blocks, iters);
+    run<K_MULWIDE_BOTH>(d, blocks, iters);
+    run<K_MADWIDE_BOTH>(d, blocks, iters);
+    run<K_BFLY_V2>(d, blocks, iters);
+    run<K_BFLY_V3>(d, blocks, iters);
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { printf("cuda error %s\n", cudaGetErrorString(e)); return 1; }
     return 0;

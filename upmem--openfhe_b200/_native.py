@@ -94,6 +94,10 @@ SIGNATURES = {
     "fhe_dcrt_chain_host": (ci, [vp, ctypes.POINTER(ci), ci, vp, vp, sz]),
     "fhe_ntt_host": (ci, [vp, vp, sz, ci]),
     "fhe_imad_probe": (ci, [vp, ci, ci, ci, ctypes.POINTER(ctypes.c_float)]),
+    "fhe_decrypt_scale_create": (ci, [vp, u64, vp, vp, vp, vp, ctypes.POINTER(vp)]),
+    "fhe_decrypt_scale_destroy": (ci, [vp]),
+    "fhe_decrypt_scale_tables": (ci, [vp, vp, vp, vp, vp, ctypes.POINTER(ci)]),
+    "fhe_scale_and_round_native": (ci, [vp, u64, u64, sz, ci]),
     "fhe_keyswitch_create": (ci, [vp, u32, u32, ctypes.POINTER(vp)]),
     "fhe_keyswitch_destroy": (ci, [vp]),
     "fhe_keyswitch_digits": (u32, [vp]),

@@ -102,6 +102,18 @@ cudaError_t launch_rescale_spread(uint64_t* tmp, const uint64_t* last, size_t ba
 // digits [np][batch][T][N], keys [np][T][N], outputs [batch][T][N] over the ring r
 cudaError_t launch_ks_inner(const RingDev& r, uint64_t* o0, uint64_t* o1, const uint64_t* digits, const uint64_t* kb,
                             const uint64_t* ka, uint32_t np, size_t batch, cudaStream_t st);
+// DCRTPolyImpl::ScaleAndRound(t, ...) -> NativePoly (dcrtpoly-impl.h:1537-1816), BFV decryption
+struct DecryptDev {
+    uint32_t T;                  // towers of Q
+    uint64_t t;                  // plaintext modulus
+    uint32_t pow2, split, reduce, hbits;     // the reference's branch: t power of two; x split at hbits = qMSB/2; products reduced mod t
+    const ulonglong4* k;         // [T] {tQHatInvModqDivqModt, its Shoup companion, tQHatInvModqBDivqModt, its companion}
+    const double2* f;            // [T] {tQHatInvModqDivqFrac, tQHatInvModqBDivqFrac}
+    double td, tinv;             // double(t), 1. / td
+};
+// dst [batch][N] = ScaleAndRound of src [batch][T][N] (COEFFICIENT)
+cudaError_t launch_decrypt_scale(const DecryptDev& dd, uint64_t* dst, const uint64_t* src, size_t batch, uint32_t logN,
+                                 cudaStream_t st);
 // Counter-based uniform fill in [0, q_t) per tower (same definition as the test oracle's generator).
 cudaError_t launch_fill_uniform(const RingDev& r, uint64_t* dst, size_t batch, uint64_t seed,
                                 cudaStream_t st);

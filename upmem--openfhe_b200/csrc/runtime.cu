@@ -1791,6 +1791,115 @@ extern "C" int fhe_imad_probe(fhe_ctx* ctx, int blocks, int threads, int iters, 
 }
 
 // ---------------------------------------------------------------------------------------------
+// BFV decryption: DCRTPolyImpl::ScaleAndRound(t, ...) -> NativePoly (dcrtpoly-impl.h:1537-1816)
+// ---------------------------------------------------------------------------------------------
+struct fhe_decrypt_scale {
+    fhe_ctx* ctx = nullptr;
+    fhe_ring* ring = nullptr;
+    DecryptDev dev{};
+    std::vector<uint64_t> modt, bmodt;
+    std::vector<double> frac, bfrac;
+    void *d_k = nullptr, *d_f = nullptr;
+};
+
+extern "C" int fhe_decrypt_scale_destroy(fhe_decrypt_scale* p) {
+    if (!p) return FHE_OK;
+    cudaSetDevice(p->ctx->device);
+    if (p->d_k) arena_park(p->ctx, p->d_k);
+    if (p->d_f) arena_park(p->ctx, p->d_f);
+    delete p;
+    return FHE_OK;
+}
+
+extern "C" int fhe_decrypt_scale_create(fhe_ring* ring, uint64_t t, const uint64_t* modt, const uint64_t* b_modt,
+                                        const double* frac, const double* b_frac, fhe_decrypt_scale** out) {
+    if (!ring || !out) return fail(FHE_EINVAL, "fhe_decrypt_scale_create: null argument");
+    *out = nullptr;
+    if (t < 2 || t >= (1ull << 60)) return fail(FHE_EINVAL, "fhe_decrypt_scale_create: plaintext modulus %llu not in [2, 2^60)", (unsigned long long)t);
+    const auto& q = ring->q;
+    const uint32_t T = (uint32_t)q.size();
+    if ((modt == nullptr) != (frac == nullptr) || (b_modt == nullptr) != (b_frac == nullptr))
+        return fail(FHE_EINVAL, "fhe_decrypt_scale_create: pass the integer and the fractional table of a pair together");
+    // the reference's branch (dcrtpoly-impl.h:1546-1556, 1628-1631): bit lengths of q_0, t and the tower count
+    const unsigned qMSB = host::msb(q[0]), tMSB = host::msb(t), sMSB = host::msb(T);
+    auto* p = new fhe_decrypt_scale;
+    p->ctx = ring->ctx; p->ring = ring;
+    DecryptDev& d = p->dev;
+    d.T = T; d.t = t;
+    d.pow2 = (t & (t - 1)) == 0;
+    d.split = !(qMSB + sMSB < 52);
+    d.hbits = qMSB >> 1;
+    const unsigned width = (d.split ? d.hbits : qMSB) + tMSB + sMSB;
+    d.reduce = d.pow2 ? !(width < (d.split ? 62u : 63u)) : !(width < 52u);
+    d.td = (double)t;
+    d.tinv = 1. / d.td;
+    if (d.split && modt && !b_modt) {
+        delete p;
+        return fail(FHE_EINVAL, "fhe_decrypt_scale_create: these moduli take the split branch (qMSB + sizeQMSB >= 52): the B tables are needed");
+    }
+    p->modt.assign(T, 0); p->bmodt.assign(T, 0); p->frac.assign(T, 0.0); p->bfrac.assign(T, 0.0);
+    for (uint32_t i = 0; i < T; i++) {
+        if (modt) {
+            p->modt[i] = modt[i]; p->frac[i] = frac[i];
+            if (b_modt) { p->bmodt[i] = b_modt[i]; p->bfrac[i] = b_frac[i]; }
+            continue;
+        }
+        // bfvrns-cryptoparameters.cpp:447-494 with 128-bit integers: X = [(Q/q_i)^-1]_{q_i} * t = D * q_i + R
+        const uint64_t qi = q[i], h = prod_mod(q, i, qi);
+        if (h == 0 || std::__gcd(h, qi) != 1) { delete p; return fail(FHE_EINVAL, "fhe_decrypt_scale_create: moduli are not pairwise coprime (tower %u)", i); }
+        const host::u128 X = (host::u128)host::invmod(h, qi) * t;
+        const host::u128 D = X / qi;
+        const uint64_t R = (uint64_t)(X % qi);
+        p->modt[i] = (uint64_t)(D % t);
+        p->frac[i] = static_cast<double>((int64_t)R) / static_cast<double>((int64_t)qi);
+        if (d.split) {                               // (X << hbits) = (D << hbits) * q_i + (R << hbits)
+            const host::u128 RB = (host::u128)R << d.hbits;
+            const uint64_t two_h = (uint64_t)(((host::u128)1 << d.hbits) % t);
+            p->bmodt[i] = (uint64_t)(((host::u128)(uint64_t)(D % t) * two_h + (RB / qi) % t) % t);
+            p->bfrac[i] = static_cast<double>((int64_t)(uint64_t)(RB % qi)) / static_cast<double>((int64_t)qi);
+        }
+    }
+    for (uint32_t i = 0; i < T; i++)
+        if (p->modt[i] >= t || p->bmodt[i] >= t) { delete p; return fail(FHE_EINVAL, "fhe_decrypt_scale_create: a table entry is not reduced modulo t"); }
+    std::vector<ulonglong4> k(T);
+    std::vector<double2> f(T);
+    for (uint32_t i = 0; i < T; i++) {
+        k[i] = make_ulonglong4(p->modt[i], host::shoup_companion(p->modt[i], t), p->bmodt[i], host::shoup_companion(p->bmodt[i], t));
+        f[i] = make_double2(p->frac[i], p->bfrac[i]);
+    }
+    CUDA_TRY(cudaSetDevice(p->ctx->device));
+    int rc;
+    if ((rc = upload(p->ctx, k, &p->d_k)) || (rc = upload(p->ctx, f, &p->d_f))) { fhe_decrypt_scale_destroy(p); return rc; }
+    d.k = (const ulonglong4*)p->d_k;
+    d.f = (const double2*)p->d_f;
+    *out = p;
+    return FHE_OK;
+}
+
+extern "C" int fhe_decrypt_scale_tables(const fhe_decrypt_scale* p, uint64_t* modt, uint64_t* b_modt, double* frac, double* b_frac,
+                                        int* branch) {
+    if (!p) return fail(FHE_EINVAL, "null plan");
+    const size_t T = p->modt.size();
+    if (modt) memcpy(modt, p->modt.data(), T * 8);
+    if (b_modt) memcpy(b_modt, p->bmodt.data(), T * 8);
+    if (frac) memcpy(frac, p->frac.data(), T * 8);
+    if (b_frac) memcpy(b_frac, p->bfrac.data(), T * 8);
+    if (branch) *branch = (p->dev.pow2 ? 4 : 0) | (p->dev.split ? 2 : 0) | (p->dev.reduce ? 1 : 0);
+    return FHE_OK;
+}
+
+extern "C" int fhe_scale_and_round_native(fhe_decrypt_scale* p, fhe_dptr dst, fhe_dptr src, size_t batch, int stream) {
+    if (!p) return fail(FHE_EINVAL, "null plan");
+    StreamRef s;
+    int rc = ring_stream(p->ring, stream, &s);
+    if (rc) return rc;
+    if (batch == 0) return FHE_OK;
+    if (!dst || !src) return fail(FHE_EINVAL, "fhe_scale_and_round_native: null device pointer");
+    CUDA_TRY(launch_decrypt_scale(p->dev, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, batch, p->ring->dev.logN, s));
+    return FHE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // hybrid key switching as one device composition (KeySwitchHYBRID, src/pke/lib/keyswitch/keyswitch-hybrid.cpp:324-480)
 // ---------------------------------------------------------------------------------------------
 struct fhe_keyswitch {

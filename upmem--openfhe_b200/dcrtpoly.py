@@ -759,3 +759,37 @@ class KeySwitch:
     def __call__(self, ct0, ct1, c, evk_b, evk_a, batch, t=0, stream=0):
         """KeySwitchCore: ct0, ct1 over Ql."""
         N.check(N.lib.fhe_keyswitch_hybrid(self.h, ct0, ct1, c, evk_b, evk_a, batch, int(t), stream))
+
+
+class DecryptScale:
+    """BFV decryption's scaling step, DCRTPolyImpl::ScaleAndRound(t, ...) -> NativePoly (dcrtpoly-impl.h:1537-1816):
+    src over `ring` (COEFFICIENT) -> [batch][N] values modulo t.  tables = (modt, b_modt, frac, b_frac) as the scheme
+    holds them (bfvrns-cryptoparameters.cpp:447-494), or None to have them derived from the moduli."""
+
+    def __init__(self, ring, t, tables=None):
+        self.ring, self.t = ring, int(t)
+        h = ctypes.c_void_p()
+        if tables is None:
+            args = (None, None, None, None)
+        else:
+            self._keep = [np.ascontiguousarray(tables[0], np.uint64), np.ascontiguousarray(tables[1], np.uint64),
+                          np.ascontiguousarray(tables[2], np.float64), np.ascontiguousarray(tables[3], np.float64)]
+            args = (_ptr(self._keep[0]), _ptr(self._keep[1]), _ptr(self._keep[2]), _ptr(self._keep[3]))
+        N.check(N.lib.fhe_decrypt_scale_create(ring.h, self.t, args[0], args[1], args[2], args[3], ctypes.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_decrypt_scale_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        T = self.ring.towers
+        modt, bmodt = np.zeros(T, np.uint64), np.zeros(T, np.uint64)
+        frac, bfrac = np.zeros(T, np.float64), np.zeros(T, np.float64)
+        br = ctypes.c_int()
+        N.check(N.lib.fhe_decrypt_scale_tables(self.h, _ptr(modt), _ptr(bmodt), _ptr(frac), _ptr(bfrac), ctypes.byref(br)))
+        return modt, bmodt, frac, bfrac, br.value
+
+    def __call__(self, dst, src, batch, stream=0):
+        N.check(N.lib.fhe_scale_and_round_native(self.h, dst, src, batch, stream))
