@@ -15,6 +15,7 @@
 // traffic is 8 B per source tower and 8 B per target tower per coefficient.
 // tower_affine_kernel / rescale_spread_kernel: one pass, 128-bit loads and stores, HBM-bound.
 #include <stdlib.h>
+#include <algorithm>
 #include "modarith.cuh"
 #include "kernels.h"
 
@@ -297,12 +298,17 @@ static cudaError_t launch_basis_switch_t(const BasisDev& bd, u64* d, uint32_t ds
     return cudaGetLastError();
 }
 
+bool basis_switch_tc_applies(const BasisDev& bd, uint32_t logN);
+static cudaError_t launch_basis_switch_tc(const BasisDev& bd, u64* d, uint32_t dstT, uint32_t dst0, const u64* s, uint32_t srcT,
+                                          uint32_t src0, size_t items, uint32_t logN, bool exact, cudaStream_t st);
+
 cudaError_t launch_basis_switch(const BasisDev& bd, uint64_t* dst, uint32_t dstT, uint32_t dst0, const uint64_t* src,
                                 uint32_t srcT, uint32_t src0, size_t batch, uint32_t logN, bool exact, cudaStream_t st) {
     size_t items = batch << logN;
     if (items == 0) return cudaSuccess;
     u64* d = reinterpret_cast<u64*>(dst);
     const u64* s = reinterpret_cast<const u64*>(src);
+    if (basis_switch_tc_applies(bd, logN)) return launch_basis_switch_tc(bd, d, dstT, dst0, s, srcT, src0, items, logN, exact, st);
     return exact ? launch_basis_switch_t<true>(bd, d, dstT, dst0, s, srcT, src0, items, logN, st)
                  : launch_basis_switch_t<false>(bd, d, dstT, dst0, s, srcT, src0, items, logN, st);
 }
@@ -621,6 +627,217 @@ cudaError_t launch_tower_scale(int mode, uint64_t* out, const uint64_t* x, size_
         unsigned grid = (unsigned)(g > 148 * 64 ? 148 * 64 : g);
         if (mode == 0) tower_scale_kernel<0><<<grid, 256, 0, st>>>(o, xx, npairs, logN, sl, T, mods, k);
         else tower_scale_kernel<1><<<grid, 256, 0, st>>>(o, xx, npairs, logN, sl, T, mods, k);
+    }
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
+}
+
+
+
+// ------------------------------------------------------------------------------------------------------------------
+// The same conversion on the 5th-generation tensor cores (tcgen05.mma kind::i8, accumulators in TMEM).
+//
+// sum_i y_i * [Q/q_i]_{p_j} for all coefficients of a tile and all target towers IS a matrix product — the one dense
+// contraction on this path.  Both factors are cut into 8-bit limbs, y_i = sum_a y_ia 2^(8a), h_ij = sum_b h_ijb 2^(8b):
+//     sum_i y_i h_ij = sum_d 2^(8d) * D[j][d],    D[j][d] = sum_i sum_{a+b=d} y_ia * h_ijb        (d = 0..14)
+// and D = A x B^T with
+//     A [128 coefficients][K = 8 * sq]      A[m][8i + a] = y_ia                       (built per tile in shared memory)
+//     B [16 * targets]  [K]                 B[16j + d][8i + a] = h_ij(d-a) or 0       (a Toeplitz expansion of the table,
+//                                                                                      built once per basis on the host)
+// u8 x u8 products accumulated in s32: sq <= 32 gives 32 * 8 * 255^2 < 2^25 per entry, far from overflow.  The epilogue
+// reads the 15 diagonals of a target from TMEM (tcgen05.ld), joins them into the 128-bit sum and reduces it with the same
+// reduce128 as the integer kernel, so every value stored is the canonical residue the CPU path produces.
+//
+// One CTA = 128 threads = one 128-coefficient tile at a time (thread m owns row m: it forms the y_i of its coefficient
+// with Shoup products, writes them as 16-byte rows of the canonical K-major core-matrix layout — no swizzle: chunk kc of
+// 16 bytes of K at kc * 2048 + m * 16 — and later reads lane m of TMEM).  One elected thread issues K/32 MMAs
+// (M = 128, N = 16 * targets <= 256, K = 32 each) and commits them to an mbarrier.  Two CTAs per SM (256 TMEM columns
+// each) overlap one another's phases.  Operands: shared memory descriptors built by hand (version 1, SWIZZLE_NONE,
+// leading-dimension byte offset = the distance of the two K chunks, stride-dimension byte offset = 128 = one 8-row core
+// matrix), instruction descriptor = {C s32, A/B unsigned 8-bit, K-major both, N >> 3, M >> 4}.
+// ------------------------------------------------------------------------------------------------------------------
+constexpr int TC_M = 128;
+constexpr u32 TC_COLS = 256;                       // TMEM columns per CTA (power of two >= N)
+
+__device__ __forceinline__ u32 tc_smem(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ u64 tc_desc(u32 saddr, u32 lbo_bytes, u32 sbo_bytes) {
+    return (u64)((saddr >> 4) & 0x3fffu) | ((u64)((lbo_bytes >> 4) & 0x3fffu) << 16) | ((u64)((sbo_bytes >> 4) & 0x3fffu) << 32) |
+           (1ull << 46);                           // version 1 (Blackwell); base offset 0, SWIZZLE_NONE
+}
+
+template <bool EXACT>
+__global__ void __launch_bounds__(TC_M, 2)
+basis_switch_tc_kernel(u64* __restrict__ dst, const u64* __restrict__ src, u32 tiles, u32 logN, BasisDev bd, u32 srcT, u32 src0,
+                       u32 dstT, u32 dst0) {
+    extern __shared__ __align__(1024) unsigned char tcsm[];
+    const u32 kpad = bd.tc_kpad, jg = bd.tc_jg, ngemm = 16 * jg;
+    unsigned char* sA = tcsm;                                        // [kpad/16][128][16]
+    unsigned char* sB = sA + (size_t)kpad * TC_M;                    // [kpad/16][ngemm][16]
+    u64* sQ = reinterpret_cast<u64*>(sB + (size_t)kpad * ngemm);     // [sq]
+    u64* sC = sQ + bd.sq;                                            // [sq][2]
+    double* sI = reinterpret_cast<double*>(sC + 2 * bd.sq);          // [sq]
+    TargetMod* sT = reinterpret_cast<TargetMod*>(sI + bd.sq);        // [jg]
+    u64* bar = reinterpret_cast<u64*>(sT + jg);
+    u32* tslot = reinterpret_cast<u32*>(bar + 1);
+    const u32 tid = threadIdx.x, warp = tid >> 5;
+    const u32 j0 = blockIdx.y * jg;
+    const u32 nj = bd.sp - j0 < jg ? bd.sp - j0 : jg;                // targets of this group
+
+    // ---- setup: TMEM, barrier, the group's B matrix, constants ----
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem(tslot)), "r"(TC_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tc_smem(bar)));
+        asm volatile("fence.mbarrier_init.release.cluster;");
+    }
+    {
+        const uint4* gB = reinterpret_cast<const uint4*>(bd.tc_b + (size_t)blockIdx.y * kpad * ngemm);
+        uint4* s4 = reinterpret_cast<uint4*>(sB);
+        for (u32 k = tid; k < kpad * ngemm / 16; k += TC_M) s4[k] = gB[k];
+        uint4* a4 = reinterpret_cast<uint4*>(sA);
+        for (u32 k = tid; k < kpad * TC_M / 16; k += TC_M) a4[k] = make_uint4(0, 0, 0, 0);     // K padding stays zero
+    }
+    for (u32 i = tid; i < bd.sq; i += TC_M) {
+        sQ[i] = bd.q[i];
+        sC[2 * i] = bd.pre[i].x;
+        sC[2 * i + 1] = bd.pre[i].y;
+        sI[i] = EXACT ? bd.qinv[i] : 0.0;
+    }
+    if (tid < nj) {
+        const BasisTarget g = bd.tgt[j0 + tid];
+        sT[tid] = TargetMod{g.p, g.c64, g.c64p, g.pinv, g.post, g.postp};
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const u32 tmem = *tslot;
+    const u32 idesc = (2u << 4) | ((ngemm >> 3) << 17) | ((TC_M >> 4) << 24);      // C = s32, A / B unsigned 8-bit, K-major
+    const u32 aBase = tc_smem(sA), bBase = tc_smem(sB);
+    u32 phase = 0;
+
+    // the residues of a tile are fetched one tile ahead: the loads of tile t + 1 fly during the MMA and the epilogue of tile t
+    u64 xr[32];
+    auto fetch = [&](u32 t) {
+        const size_t e = (size_t)t * TC_M + tid;
+        const u64* sp = src + ((((e >> logN) * srcT) + src0) << logN) + ((u32)e & ((1u << logN) - 1));
+#pragma unroll
+        for (int i = 0; i < 32; i++) xr[i] = (u32)i < bd.sq ? sp[(size_t)i << logN] : 0ull;
+    };
+    if (blockIdx.x < tiles) fetch(blockIdx.x);
+    for (u32 t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const size_t e = (size_t)t * TC_M + tid;
+        const size_t b = e >> logN;
+        const u32 n = (u32)e & ((1u << logN) - 1);
+        // ---- prologue: y_i of this thread's coefficient, two towers per 16-byte row chunk ----
+        double nu = 0.5;
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+            if ((u32)i < bd.sq) {
+                const u64 y0 = shoup(xr[i], sC[2 * i], sC[2 * i + 1], sQ[i]);
+                u64 y1 = 0;
+                if (EXACT) nu = __dadd_rn(nu, __dmul_rn(__ull2double_rn(y0), sI[i]));
+                if ((u32)i + 1 < bd.sq) {
+                    y1 = shoup(xr[i + 1], sC[2 * i + 2], sC[2 * i + 3], sQ[i + 1]);
+                    if (EXACT) nu = __dadd_rn(nu, __dmul_rn(__ull2double_rn(y1), sI[i + 1]));
+                }
+                *reinterpret_cast<ulonglong2*>(sA + (size_t)(i >> 1) * (TC_M * 16) + tid * 16) = make_ulonglong2(y0, y1);
+            }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> visible to the tensor core
+        asm volatile("tcgen05.fence::before_thread_sync;");
+        __syncthreads();
+        // ---- one thread issues the MMAs of the tile and commits them to the barrier ----
+        if (tid == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;");
+            for (u32 kb = 0; kb < kpad / 32; kb++) {
+                const u64 da = tc_desc(aBase + kb * 2 * (TC_M * 16), TC_M * 16, 128);
+                const u64 db = tc_desc(bBase + kb * 2 * (ngemm * 16), ngemm * 16, 128);
+                const u32 acc = kb ? 1u : 0u;
+                asm volatile(
+                    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                    "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                    ::"r"(tmem), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(tc_smem(bar)) : "memory");
+        }
+        if (t + gridDim.x < tiles) fetch(t + gridDim.x);
+        {   // everyone waits for the accumulators (bounded: a barrier that never completes traps instead of hanging the GPU)
+            const u32 baddr = tc_smem(bar);
+            u32 done = 0, spins = 0;
+            while (!done) {
+                asm volatile(
+                    "{\n\t.reg .pred P1;\n\t"
+                    "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2, %3;\n\t"
+                    "selp.u32 %0, 1, 0, P1;\n\t}" : "=r"(done) : "r"(baddr), "r"(phase), "r"(1000000u) : "memory");
+                if (!done && ++spins > 4000u) __trap();
+            }
+            phase ^= 1;
+        }
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        // ---- epilogue: the 15 diagonals of every target of this group, from TMEM lane `tid` ----
+        const u32 alpha = EXACT ? (u32)nu : 0u;
+        auto tload = [&](u32 (&d)[16], u32 jj) {
+            const u32 taddr = tmem + ((warp * 32u) << 16) + jj * 16u;
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                         : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7]), "=r"(d[8]),
+                           "=r"(d[9]), "=r"(d[10]), "=r"(d[11]), "=r"(d[12]), "=r"(d[13]), "=r"(d[14]), "=r"(d[15])
+                         : "r"(taddr));
+        };
+        auto finish = [&](const u32 (&d)[16], u32 jj) {
+            // sum_d d[d] * 2^(8d): three 64-bit partial sums (five diagonals each, below 2^58), joined at bits 0, 40, 80
+            const u64 s0 = (u64)d[0] + ((u64)d[1] << 8) + ((u64)d[2] << 16) + ((u64)d[3] << 24) + ((u64)d[4] << 32);
+            const u64 s1 = (u64)d[5] + ((u64)d[6] << 8) + ((u64)d[7] << 16) + ((u64)d[8] << 24) + ((u64)d[9] << 32);
+            const u64 s2 = (u64)d[10] + ((u64)d[11] << 8) + ((u64)d[12] << 16) + ((u64)d[13] << 24) + ((u64)d[14] << 32);
+            const u64 lo = s0 + (s1 << 40);
+            const u64 hi = (s1 >> 24) + (s2 << 16) + (lo < s0 ? 1ull : 0ull);
+            const TargetMod tg = sT[jj];
+            u64 r = reduce128(lo, hi, tg);
+            if (tg.post) r = shoup(r, tg.post, tg.postp, tg.p);
+            if (EXACT) r = submod(r, bd.alphaq[(size_t)alpha * bd.sp + j0 + jj], tg.p);
+            dst[(((b * dstT) + dst0 + j0 + jj) << logN) + n] = r;
+        };
+        for (u32 jj = 0; jj < nj; jj += 2) {                 // two targets per TMEM round trip
+            u32 d0[16], d1[16];
+            tload(d0, jj);
+            if (jj + 1 < nj) tload(d1, jj + 1);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            finish(d0, jj);
+            if (jj + 1 < nj) finish(d1, jj + 1);
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;");
+        __syncthreads();                     // TMEM and the A tile are free for the next tile
+    }
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TC_COLS));
+}
+
+bool basis_switch_tc_applies(const BasisDev& bd, uint32_t logN) {
+    static const int mode = env_int("FHE_B200_BASIS_TC", 1);
+    return mode != 0 && bd.tc_b != nullptr && logN >= 7;
+}
+
+static cudaError_t launch_basis_switch_tc(const BasisDev& bd, u64* d, uint32_t dstT, uint32_t dst0, const u64* s, uint32_t srcT,
+                                          uint32_t src0, size_t items, uint32_t logN, bool exact, cudaStream_t st) {
+    const size_t tiles = items / TC_M;                     // N >= 128: tiles never straddle a polynomial
+    if (tiles > 0xffffffffull) return cudaErrorInvalidValue;
+    const u32 ngemm = 16 * bd.tc_jg;
+    size_t smem = (size_t)bd.tc_kpad * (TC_M + ngemm) + (size_t)bd.sq * 32 + (size_t)bd.tc_jg * sizeof(TargetMod) + 64;
+    if (smem < 80 * 1024) smem = 80 * 1024;                // two CTAs per SM, not three: each holds 256 of the 512 TMEM columns
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    unsigned gx = (unsigned)std::min<size_t>(tiles, (size_t)2 * sms / bd.tc_groups > 0 ? (size_t)2 * sms / bd.tc_groups : 1);
+    dim3 grid(gx, bd.tc_groups);
+    cudaError_t e;
+    if (exact) {
+        e = cudaFuncSetAttribute(basis_switch_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        basis_switch_tc_kernel<true><<<grid, TC_M, smem, st>>>(d, s, (u32)tiles, logN, bd, srcT, src0, dstT, dst0);
+    } else {
+        e = cudaFuncSetAttribute(basis_switch_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        basis_switch_tc_kernel<false><<<grid, TC_M, smem, st>>>(d, s, (u32)tiles, logN, bd, srcT, src0, dstT, dst0);
     }
     kernel_launch_count_add(1);
     return cudaGetLastError();

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stddef.h>
 #include <stdint.h>
+#include <vector>
 
 namespace fhe {
 
@@ -75,7 +76,14 @@ struct BasisDev {
     const double* qinv;          // [sq] 1./double(q_i)                      (exact form only)
     const uint64_t* alphaq;      // [sq+1][sp] [alpha*Q]_{p_j}               (exact form only)
     uint32_t narrow;             // 1: every q_i and every hat entry is below 2^60 -> carry-free 30-bit split accumulation
+    // tensor-core form (basis.cu, basis_switch_tc_kernel): the table expanded into 8-bit limbs, Toeplitz per target,
+    // in the shared-memory core-matrix layout, one block per group of tc_jg targets; null: integer kernels only
+    const uint8_t* tc_b;         // [tc_groups][tc_kpad / 16][16 * tc_jg][16]
+    uint32_t tc_groups, tc_jg, tc_kpad;
 };
+// host side: fills `out` ([groups][kpad/16][16*jg][16] bytes) from hat [sq][sp]; returns false when the shape is not covered
+bool basis_tc_build(const uint64_t* hat, uint32_t sq, uint32_t sp, uint32_t& groups, uint32_t& jg, uint32_t& kpad,
+                    std::vector<uint8_t>& out);
 struct ScaleDev {                // DCRTPolyImpl::ScaleAndRound(paramsOutput, ...)
     uint32_t sI, sO, in0, out0;  // input / output tower counts and their first tower inside [sI+sO]
     const double* frac;          // [sI]

@@ -957,6 +957,7 @@ struct fhe_basis {
     // ApproxModDown extras: [P^-1]_{q_i} records and the t-folded variant of pre / tgt (cached for the last t)
     void *d_pinv = nullptr, *d_pre_t = nullptr, *d_tgt_t = nullptr;
     void *d_qinv = nullptr, *d_alphaq = nullptr;   // exact form (SwitchCRTBasis): 1/q_i and [alpha*Q]_{p_j}
+    void* d_tc = nullptr;                          // the table as 8-bit limbs for the tensor-core kernel (basis.cu)
     uint64_t t_cached = 0;
     bool pinv_ready = false;
     Scratch s0, s1;
@@ -980,11 +981,36 @@ static void basis_fill(const fhe_basis* b, uint64_t t, std::vector<ulonglong2>& 
     }
 }
 
+// The [Q/q_i]_{p_j} table as the B operand of basis_switch_tc_kernel: 8-bit limbs, Toeplitz per target
+// (row 16j + d, column 8i + a holds limb d - a of the entry), stored in the kernel's shared-memory layout
+// (16-byte K chunks, chunk-major), one block per group of at most 16 targets.
+bool fhe::basis_tc_build(const uint64_t* hat, uint32_t sq, uint32_t sp, uint32_t& groups, uint32_t& jg, uint32_t& kpad,
+                         std::vector<uint8_t>& out) {
+    if (sq == 0 || sq > 32 || sp == 0) return false;
+    const uint32_t ng = (sp + 15) / 16;
+    jg = (sp + ng - 1) / ng;
+    groups = (sp + jg - 1) / jg;
+    kpad = (8 * sq + 31) / 32 * 32;
+    const uint32_t ngemm = 16 * jg;
+    out.assign((size_t)groups * kpad * ngemm, 0);
+    for (uint32_t g = 0; g < groups; g++)
+        for (uint32_t jj = 0; jj < jg && g * jg + jj < sp; jj++)
+            for (uint32_t i = 0; i < sq; i++) {
+                const uint64_t h = hat[(size_t)i * sp + g * jg + jj];
+                for (uint32_t a = 0; a < 8; a++)
+                    for (uint32_t bb = 0; bb < 8; bb++) {
+                        const uint32_t d = a + bb, k = 8 * i + a, nrow = 16 * jj + d;
+                        out[(size_t)g * kpad * ngemm + ((size_t)(k / 16) * ngemm + nrow) * 16 + (k % 16)] = (uint8_t)(h >> (8 * bb));
+                    }
+            }
+    return true;
+}
+
 extern "C" int fhe_basis_destroy(fhe_basis* b) {
     if (!b) return FHE_OK;
     cudaSetDevice(b->ctx->device);
     cudaDeviceSynchronize();
-    for (void* p : {b->d_q, b->d_pre, b->d_hat, b->d_tgt, b->d_pinv, b->d_pre_t, b->d_tgt_t, b->d_qinv, b->d_alphaq})
+    for (void* p : {b->d_q, b->d_pre, b->d_hat, b->d_tgt, b->d_pinv, b->d_pre_t, b->d_tgt_t, b->d_qinv, b->d_alphaq, b->d_tc})
         if (p) arena_park(b->ctx, p);
     b->s0.drop(b->ctx);
     b->s1.drop(b->ctx);
@@ -1035,6 +1061,15 @@ extern "C" int fhe_basis_create(fhe_ring* from, fhe_ring* to, const uint64_t* qh
     b->dev.hat = (const uint64_t*)b->d_hat;
     b->dev.tgt = (const BasisTarget*)b->d_tgt;
     b->dev.narrow = !basis_force_wide() && all_below_2_60(from->q) && all_below_2_60(b->hat_modp);
+    {   // tensor-core form of the table (sq <= 32; ring dimension checked at launch)
+        std::vector<uint8_t> tc;
+        uint32_t groups = 0, jg = 0, kpad = 0;
+        if (basis_tc_build(b->hat_modp.data(), (uint32_t)sq, (uint32_t)sp, groups, jg, kpad, tc)) {
+            if ((rc = upload(b->ctx, tc, &b->d_tc))) { fhe_basis_destroy(b); return rc; }
+            b->dev.tc_b = (const uint8_t*)b->d_tc;
+            b->dev.tc_groups = groups; b->dev.tc_jg = jg; b->dev.tc_kpad = kpad;
+        }
+    }
     *out = b;
     return FHE_OK;
 }
