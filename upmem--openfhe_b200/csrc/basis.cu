@@ -657,7 +657,6 @@ cudaError_t launch_tower_scale(int mode, uint64_t* out, const uint64_t* x, size_
 // matrix), instruction descriptor = {C s32, A/B unsigned 8-bit, K-major both, N >> 3, M >> 4}.
 // ------------------------------------------------------------------------------------------------------------------
 constexpr int TC_M = 128;
-constexpr u32 TC_COLS = 256;                       // TMEM columns per CTA (power of two >= N)
 
 __device__ __forceinline__ u32 tc_smem(const void* p) { return (u32)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ u64 tc_desc(u32 saddr, u32 lbo_bytes, u32 sbo_bytes) {
@@ -665,45 +664,61 @@ __device__ __forceinline__ u64 tc_desc(u32 saddr, u32 lbo_bytes, u32 sbo_bytes) 
            (1ull << 46);                           // version 1 (Blackwell); base offset 0, SWIZZLE_NONE
 }
 
-template <bool EXACT>
-__global__ void __launch_bounds__(TC_M, 2)
+// A CTA holds SUB independent sub-CTAs of 128 * TPR threads (own A tile, own accumulator columns in TMEM, own mbarrier,
+// own named barrier), which share the B matrix and the constants: SUB tiles are in flight per SM, and while one sub-CTA
+// waits for its MMAs or reads TMEM the others run their Shoup products.  TPR threads share a row of a tile: thread
+// `st` of a sub-CTA owns row m = st % 128 together with st + 128, ...; they split the source towers of the prologue
+// (pairs of towers, round robin) and the targets of the epilogue between them (all of them sit in warps with the same
+// index modulo 4, i.e. in the TMEM lane quarter of their row).
+template <bool EXACT, int TPR, int SUB>
+__global__ void __launch_bounds__(TC_M * TPR * SUB, SUB == 1 ? 2 : 1)
 basis_switch_tc_kernel(u64* __restrict__ dst, const u64* __restrict__ src, u32 tiles, u32 logN, BasisDev bd, u32 srcT, u32 src0,
                        u32 dstT, u32 dst0) {
+    constexpr int STHREADS = TC_M * TPR, THREADS = STHREADS * SUB;
+    constexpr int PP = (16 + TPR - 1) / TPR;                         // tower pairs per thread (sq <= 32)
+    constexpr u32 TCOLS = SUB == 1 ? 256u : 512u;                    // SUB = 1: two CTAs per SM, half of TMEM each
     extern __shared__ __align__(1024) unsigned char tcsm[];
     const u32 kpad = bd.tc_kpad, jg = bd.tc_jg, ngemm = 16 * jg;
-    unsigned char* sA = tcsm;                                        // [kpad/16][128][16]
-    unsigned char* sB = sA + (size_t)kpad * TC_M;                    // [kpad/16][ngemm][16]
-    u64* sQ = reinterpret_cast<u64*>(sB + (size_t)kpad * ngemm);     // [sq]
-    u64* sC = sQ + bd.sq;                                            // [sq][2]
-    double* sI = reinterpret_cast<double*>(sC + 2 * bd.sq);          // [sq]
-    TargetMod* sT = reinterpret_cast<TargetMod*>(sI + bd.sq);        // [jg]
-    u64* bar = reinterpret_cast<u64*>(sT + jg);
-    u32* tslot = reinterpret_cast<u32*>(bar + 1);
-    const u32 tid = threadIdx.x, warp = tid >> 5;
+    const u32 cstride = (ngemm + 31) & ~31u;                         // accumulator columns per sub-CTA
+    unsigned char* sB = tcsm;                                        // [kpad/16][ngemm][16], shared by the sub-CTAs
+    unsigned char* sAall = sB + (size_t)kpad * ngemm;                // SUB x [kpad/16][128][16]
+    u64* sQ = reinterpret_cast<u64*>(sAall + (size_t)SUB * kpad * TC_M);   // [32]
+    u64* sC = sQ + 32;                                               // [32][2]
+    double* sI = reinterpret_cast<double*>(sC + 64);                 // [32]
+    TargetMod* sT = reinterpret_cast<TargetMod*>(sI + 32);           // [16]
+    u64* bars = reinterpret_cast<u64*>(sT + 16);                     // [SUB]
+    u32* tslot = reinterpret_cast<u32*>(bars + 4);
+    double* sPall = reinterpret_cast<double*>(bars + 6);             // EXACT: SUB x [32][128] the terms of nu, summed in index order
+    const u32 tid = threadIdx.x, sub = tid / STHREADS, st = tid % STHREADS;
+    const u32 warp = tid >> 5, row = st & (TC_M - 1), part = st >> 7;
+    unsigned char* sA = sAall + (size_t)sub * kpad * TC_M;
+    double* sP = sPall + (size_t)sub * 32 * TC_M;
+    u64* bar = bars + sub;
     const u32 j0 = blockIdx.y * jg;
     const u32 nj = bd.sp - j0 < jg ? bd.sp - j0 : jg;                // targets of this group
 
-    // ---- setup: TMEM, barrier, the group's B matrix, constants ----
+    // ---- setup: TMEM, barriers, the group's B matrix, constants ----
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem(tslot)), "r"(TC_COLS));
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem(tslot)), "r"(TCOLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
-    if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tc_smem(bar)));
+    if (tid < SUB) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tc_smem(bars + tid)));
         asm volatile("fence.mbarrier_init.release.cluster;");
     }
     {
         const uint4* gB = reinterpret_cast<const uint4*>(bd.tc_b + (size_t)blockIdx.y * kpad * ngemm);
         uint4* s4 = reinterpret_cast<uint4*>(sB);
-        for (u32 k = tid; k < kpad * ngemm / 16; k += TC_M) s4[k] = gB[k];
-        uint4* a4 = reinterpret_cast<uint4*>(sA);
-        for (u32 k = tid; k < kpad * TC_M / 16; k += TC_M) a4[k] = make_uint4(0, 0, 0, 0);     // K padding stays zero
+        for (u32 k = tid; k < kpad * ngemm / 16; k += THREADS) s4[k] = gB[k];
+        uint4* a4 = reinterpret_cast<uint4*>(sAall);
+        for (u32 k = tid; k < SUB * kpad * TC_M / 16; k += THREADS) a4[k] = make_uint4(0, 0, 0, 0);     // K padding stays zero
     }
-    for (u32 i = tid; i < bd.sq; i += TC_M) {
-        sQ[i] = bd.q[i];
-        sC[2 * i] = bd.pre[i].x;
-        sC[2 * i + 1] = bd.pre[i].y;
-        sI[i] = EXACT ? bd.qinv[i] : 0.0;
+    for (u32 i = tid; i < 32; i += THREADS) {
+        const bool in = i < bd.sq;
+        sQ[i] = in ? bd.q[i] : 4ull;
+        sC[2 * i] = in ? bd.pre[i].x : 0ull;
+        sC[2 * i + 1] = in ? bd.pre[i].y : 0ull;
+        sI[i] = (EXACT && in) ? bd.qinv[i] : 0.0;
     }
     if (tid < nj) {
         const BasisTarget g = bd.tgt[j0 + tid];
@@ -712,44 +727,50 @@ basis_switch_tc_kernel(u64* __restrict__ dst, const u64* __restrict__ src, u32 t
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;");
-    const u32 tmem = *tslot;
+    const u32 tmem = *tslot + sub * cstride;
     const u32 idesc = (2u << 4) | ((ngemm >> 3) << 17) | ((TC_M >> 4) << 24);      // C = s32, A / B unsigned 8-bit, K-major
     const u32 aBase = tc_smem(sA), bBase = tc_smem(sB);
+    const u32 npairs = (bd.sq + 1) >> 1;
+    auto sub_sync = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(sub + 1), "n"(STHREADS) : "memory"); };
     u32 phase = 0;
+    const u32 tstep = gridDim.x * SUB, tfirst = blockIdx.x * SUB + sub;
 
     // the residues of a tile are fetched one tile ahead: the loads of tile t + 1 fly during the MMA and the epilogue of tile t
-    u64 xr[32];
+    u64 xr[2 * PP];
     auto fetch = [&](u32 t) {
-        const size_t e = (size_t)t * TC_M + tid;
+        const size_t e = (size_t)t * TC_M + row;
         const u64* sp = src + ((((e >> logN) * srcT) + src0) << logN) + ((u32)e & ((1u << logN) - 1));
 #pragma unroll
-        for (int i = 0; i < 32; i++) xr[i] = (u32)i < bd.sq ? sp[(size_t)i << logN] : 0ull;
+        for (int k = 0; k < PP; k++) {
+            const u32 i = 2 * (part + k * TPR);
+            xr[2 * k] = i < bd.sq ? sp[(size_t)i << logN] : 0ull;
+            xr[2 * k + 1] = i + 1 < bd.sq ? sp[(size_t)(i + 1) << logN] : 0ull;
+        }
     };
-    if (blockIdx.x < tiles) fetch(blockIdx.x);
-    for (u32 t = blockIdx.x; t < tiles; t += gridDim.x) {
-        const size_t e = (size_t)t * TC_M + tid;
+    if (tfirst < tiles) fetch(tfirst);
+    for (u32 t = tfirst; t < tiles; t += tstep) {
+        const size_t e = (size_t)t * TC_M + row;
         const size_t b = e >> logN;
         const u32 n = (u32)e & ((1u << logN) - 1);
-        // ---- prologue: y_i of this thread's coefficient, two towers per 16-byte row chunk ----
-        double nu = 0.5;
+        // ---- prologue: y_i of this row, two towers per 16-byte row chunk ----
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-            if ((u32)i < bd.sq) {
-                const u64 y0 = shoup(xr[i], sC[2 * i], sC[2 * i + 1], sQ[i]);
-                u64 y1 = 0;
-                if (EXACT) nu = __dadd_rn(nu, __dmul_rn(__ull2double_rn(y0), sI[i]));
-                if ((u32)i + 1 < bd.sq) {
-                    y1 = shoup(xr[i + 1], sC[2 * i + 2], sC[2 * i + 3], sQ[i + 1]);
-                    if (EXACT) nu = __dadd_rn(nu, __dmul_rn(__ull2double_rn(y1), sI[i + 1]));
+        for (int k = 0; k < PP; k++) {
+            const u32 pr = part + k * TPR, i = 2 * pr;
+            if (pr < npairs) {
+                const u64 y0 = shoup(xr[2 * k], sC[2 * i], sC[2 * i + 1], sQ[i]);
+                const u64 y1 = i + 1 < bd.sq ? shoup(xr[2 * k + 1], sC[2 * i + 2], sC[2 * i + 3], sQ[i + 1]) : 0ull;
+                if (EXACT) {
+                    sP[i * TC_M + row] = __dmul_rn(__ull2double_rn(y0), sI[i]);
+                    sP[(i + 1) * TC_M + row] = __dmul_rn(__ull2double_rn(y1), sI[i + 1]);
                 }
-                *reinterpret_cast<ulonglong2*>(sA + (size_t)(i >> 1) * (TC_M * 16) + tid * 16) = make_ulonglong2(y0, y1);
+                *reinterpret_cast<ulonglong2*>(sA + (size_t)pr * (TC_M * 16) + row * 16) = make_ulonglong2(y0, y1);
             }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> visible to the tensor core
         asm volatile("tcgen05.fence::before_thread_sync;");
-        __syncthreads();
-        // ---- one thread issues the MMAs of the tile and commits them to the barrier ----
-        if (tid == 0) {
+        sub_sync();
+        // ---- one thread issues the MMAs of the tile and commits them to the sub-CTA's barrier ----
+        if (st == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;");
             for (u32 kb = 0; kb < kpad / 32; kb++) {
                 const u64 da = tc_desc(aBase + kb * 2 * (TC_M * 16), TC_M * 16, 128);
@@ -762,7 +783,13 @@ basis_switch_tc_kernel(u64* __restrict__ dst, const u64* __restrict__ src, u32 t
             }
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(tc_smem(bar)) : "memory");
         }
-        if (t + gridDim.x < tiles) fetch(t + gridDim.x);
+        if (t + tstep < tiles) fetch(t + tstep);
+        u32 alpha = 0;
+        if (EXACT) {                        // nu = 0.5 + sum_i double(y_i) * (1 / q_i), IEEE double in index order (:1197-1203)
+            double nu = 0.5;
+            for (u32 i = 0; i < bd.sq; i++) nu = __dadd_rn(nu, sP[i * TC_M + row]);
+            alpha = (u32)nu;
+        }
         {   // everyone waits for the accumulators (bounded: a barrier that never completes traps instead of hanging the GPU)
             const u32 baddr = tc_smem(bar);
             u32 done = 0, spins = 0;
@@ -776,10 +803,9 @@ basis_switch_tc_kernel(u64* __restrict__ dst, const u64* __restrict__ src, u32 t
             phase ^= 1;
         }
         asm volatile("tcgen05.fence::after_thread_sync;");
-        // ---- epilogue: the 15 diagonals of every target of this group, from TMEM lane `tid` ----
-        const u32 alpha = EXACT ? (u32)nu : 0u;
+        // ---- epilogue: the 15 diagonals of this thread's targets, from the TMEM lane of its row ----
         auto tload = [&](u32 (&d)[16], u32 jj) {
-            const u32 taddr = tmem + ((warp * 32u) << 16) + jj * 16u;
+            const u32 taddr = tmem + (((warp & 3u) * 32u) << 16) + jj * 16u;
             asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
                          : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7]), "=r"(d[8]),
                            "=r"(d[9]), "=r"(d[10]), "=r"(d[11]), "=r"(d[12]), "=r"(d[13]), "=r"(d[14]), "=r"(d[15])
@@ -798,18 +824,22 @@ basis_switch_tc_kernel(u64* __restrict__ dst, const u64* __restrict__ src, u32 t
             if (EXACT) r = submod(r, bd.alphaq[(size_t)alpha * bd.sp + j0 + jj], tg.p);
             dst[(((b * dstT) + dst0 + j0 + jj) << logN) + n] = r;
         };
-        for (u32 jj = 0; jj < nj; jj += 2) {                 // two targets per TMEM round trip
+        // tcgen05.ld is warp-collective (.sync.aligned): every warp runs the same number of rounds, guarded per target
+        for (u32 base = 0; base < nj; base += 2 * TPR) {
+            const u32 ja = base + part, jb = base + TPR + part;
             u32 d0[16], d1[16];
-            tload(d0, jj);
-            if (jj + 1 < nj) tload(d1, jj + 1);
+            if (ja < nj) tload(d0, ja);
+            if (jb < nj) tload(d1, jb);
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            finish(d0, jj);
-            if (jj + 1 < nj) finish(d1, jj + 1);
+            if (ja < nj) finish(d0, ja);
+            if (jb < nj) finish(d1, jb);
         }
         asm volatile("tcgen05.fence::before_thread_sync;");
-        __syncthreads();                     // TMEM and the A tile are free for the next tile
+        sub_sync();                          // the sub-CTA's TMEM columns and A tile are free for its next tile
     }
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TC_COLS));
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(*tslot), "r"(TCOLS));
 }
 
 bool basis_switch_tc_applies(const BasisDev& bd, uint32_t logN) {
@@ -817,30 +847,43 @@ bool basis_switch_tc_applies(const BasisDev& bd, uint32_t logN) {
     return mode != 0 && bd.tc_b != nullptr && logN >= 7;
 }
 
+template <bool EXACT, int TPR, int SUB>
+static cudaError_t launch_basis_switch_tc_t(const BasisDev& bd, u64* d, uint32_t dstT, uint32_t dst0, const u64* s, uint32_t srcT,
+                                            uint32_t src0, size_t tiles, uint32_t logN, cudaStream_t st) {
+    const u32 ngemm = 16 * bd.tc_jg;
+    size_t smem = (size_t)bd.tc_kpad * (SUB * TC_M + ngemm) + 32 * 32 + 16 * sizeof(TargetMod) + 48 + (EXACT ? (size_t)SUB * 32 * TC_M * 8 : 0) + 64;
+    // SUB > 1: one CTA per SM (it takes all 512 TMEM columns); SUB = 1: two CTAs per SM with 256 columns each, never three
+    const size_t floor_bytes = SUB == 1 ? 80 * 1024 : 116 * 1024;
+    if (smem < floor_bytes) smem = floor_bytes;
+    if (smem > 227 * 1024) return cudaErrorInvalidValue;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const size_t per_group = std::max<size_t>(1, (size_t)(SUB == 1 ? 2 : 1) * sms / bd.tc_groups);
+    dim3 grid((unsigned)std::min((tiles + SUB - 1) / SUB, per_group), bd.tc_groups);
+    auto kern = basis_switch_tc_kernel<EXACT, TPR, SUB>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, TC_M * TPR * SUB, smem, st>>>(d, s, (u32)tiles, logN, bd, srcT, src0, dstT, dst0);
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
+}
+
 static cudaError_t launch_basis_switch_tc(const BasisDev& bd, u64* d, uint32_t dstT, uint32_t dst0, const u64* s, uint32_t srcT,
                                           uint32_t src0, size_t items, uint32_t logN, bool exact, cudaStream_t st) {
     const size_t tiles = items / TC_M;                     // N >= 128: tiles never straddle a polynomial
     if (tiles > 0xffffffffull) return cudaErrorInvalidValue;
-    const u32 ngemm = 16 * bd.tc_jg;
-    size_t smem = (size_t)bd.tc_kpad * (TC_M + ngemm) + (size_t)bd.sq * 32 + (size_t)bd.tc_jg * sizeof(TargetMod) + 64;
-    if (smem < 80 * 1024) smem = 80 * 1024;                // two CTAs per SM, not three: each holds 256 of the 512 TMEM columns
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    unsigned gx = (unsigned)std::min<size_t>(tiles, (size_t)2 * sms / bd.tc_groups > 0 ? (size_t)2 * sms / bd.tc_groups : 1);
-    dim3 grid(gx, bd.tc_groups);
-    cudaError_t e;
-    if (exact) {
-        e = cudaFuncSetAttribute(basis_switch_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        basis_switch_tc_kernel<true><<<grid, TC_M, smem, st>>>(d, s, (u32)tiles, logN, bd, srcT, src0, dstT, dst0);
-    } else {
-        e = cudaFuncSetAttribute(basis_switch_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        basis_switch_tc_kernel<false><<<grid, TC_M, smem, st>>>(d, s, (u32)tiles, logN, bd, srcT, src0, dstT, dst0);
-    }
-    kernel_launch_count_add(1);
-    return cudaGetLastError();
+    // accumulators of 16 columns per target: three sub-CTAs fit the 512 TMEM columns up to 10 targets per group, two beyond
+    static const int sub_env = env_int("FHE_B200_BASIS_TC_SUB", 0);
+    const u32 cstride = (16 * bd.tc_jg + 31) & ~31u;
+    (void)cstride;
+    int sub = 1;                                           // measured best on the B200: two CTAs per SM, one tile each
+    if (sub_env >= 1 && sub_env <= 3 && ((u32)sub_env * cstride <= 512)) sub = sub_env;
+    if (exact && sub == 3 && (size_t)bd.tc_kpad * (3 * TC_M + 16 * bd.tc_jg) + 3 * 32 * TC_M * 8 + 4096 > 227 * 1024) sub = 2;
+#define TC_GO(E, S) launch_basis_switch_tc_t<E, 2, S>(bd, d, dstT, dst0, s, srcT, src0, tiles, logN, st)
+    if (exact) return sub == 3 ? TC_GO(true, 3) : sub == 2 ? TC_GO(true, 2) : TC_GO(true, 1);
+    return sub == 3 ? TC_GO(false, 3) : sub == 2 ? TC_GO(false, 2) : TC_GO(false, 1);
+#undef TC_GO
 }
 
 }  // namespace fhe
