@@ -812,12 +812,18 @@ basis_switch_tc_kernel(u64* __restrict__ dst, const u64* __restrict__ src, u32 t
                          : "r"(taddr));
         };
         auto finish = [&](const u32 (&d)[16], u32 jj) {
-            // sum_d d[d] * 2^(8d): three 64-bit partial sums (five diagonals each, below 2^58), joined at bits 0, 40, 80
-            const u64 s0 = (u64)d[0] + ((u64)d[1] << 8) + ((u64)d[2] << 16) + ((u64)d[3] << 24) + ((u64)d[4] << 32);
-            const u64 s1 = (u64)d[5] + ((u64)d[6] << 8) + ((u64)d[7] << 16) + ((u64)d[8] << 24) + ((u64)d[9] << 32);
-            const u64 s2 = (u64)d[10] + ((u64)d[11] << 8) + ((u64)d[12] << 16) + ((u64)d[13] << 24) + ((u64)d[14] << 32);
-            const u64 lo = s0 + (s1 << 40);
-            const u64 hi = (s1 >> 24) + (s2 << 16) + (lo < s0 ? 1ull : 0ull);
+            // sum_d d[d] * 2^(8d).  Every d[] is below 2^25, so the diagonals 4 apart tile a 128-bit number without overlap:
+            // N_r = d[r] + d[4+r] 2^32 + d[8+r] 2^64 + d[12+r] 2^96 costs nothing, and the sum is N_0 + N_1 2^8 + N_2 2^16 + N_3 2^24
+            // (three 128-bit shifts and additions; the total is below 2^125, so nothing is shifted out)
+            auto pack = [](u32 l, u32 h) { u64 v; asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "r"(l), "r"(h)); return v; };
+            u64 lo = pack(d[0], d[4]), hi = pack(d[8], d[12]);
+#pragma unroll
+            for (int r = 1; r < 4; r++) {
+                const u64 l = pack(d[r], d[4 + r]), h = pack(d[8 + r], r == 3 ? 0u : d[12 + r]);
+                const u64 ls = l << (8 * r), hs = (h << (8 * r)) | (l >> (64 - 8 * r));
+                lo += ls;
+                hi += hs + (lo < ls ? 1ull : 0ull);
+            }
             const TargetMod tg = sT[jj];
             u64 r = reduce128(lo, hi, tg);
             if (tg.post) r = shoup(r, tg.post, tg.postp, tg.p);
