@@ -101,6 +101,10 @@ int fhe_sync(fhe_ctx* ctx, int stream);               /* stream = -2: whole devi
 long fhe_launch_count(void);
 
 /* ---- memory ------------------------------------------------------------------------------- */
+/* Alignment: fhe_alloc returns 256-byte aligned blocks.  The polynomial kernels move 128-bit words, so every
+ * polynomial pointer handed to an entry point below (a block, or a view into one at a whole number of towers) must be
+ * 16-byte aligned when N >= 2; a pointer that is not is refused with FHE_EINVAL, never passed to a kernel.  The flat
+ * fhe_vec_* entry points take any 8-byte aligned pointer (they fall back to a scalar element loop). */
 int fhe_alloc(fhe_ctx* ctx, size_t bytes, fhe_dptr* out);        /* 256-byte aligned */
 /* Stream-ordered: a block may be freed as soon as the calls that use it have RETURNED (their launches may still be
  * pending).  It is handed out again only after everything enqueued, before the fhe_free call, on the streams of this
@@ -144,7 +148,7 @@ int fhe_dcrt_op(fhe_ring* ring, int op, fhe_dptr dst, fhe_dptr a, fhe_dptr b, si
 int fhe_ntt_forward(fhe_ring* ring, fhe_dptr x, size_t batch, int stream);
 int fhe_ntt_inverse(fhe_ring* ring, fhe_dptr x, size_t batch, int stream);
 /* same, selecting the kernel family: 0 auto, 1 single-CTA shared-memory kernel (N <= 4096), 2 one-tile-per-CTA two-pass
- * kernels, 3 warp-specialised persistent two-pass kernels (N = 2^14..2^16; what auto picks for large batches) */
+ * kernels, 3 warp-specialised persistent two-pass kernels (N = 2^14..2^16; measured slower, never picked by auto) */
 int fhe_ntt_algo(fhe_ring* ring, fhe_dptr x, size_t batch, int inverse, int algo, int stream);
 /* c = INTT(NTT(a) .* NTT(b)): negacyclic product of COEFFICIENT-format polynomials; a and b are
  * left in EVALUATION format (they are transformed in place), c may alias neither. */

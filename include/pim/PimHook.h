@@ -432,15 +432,28 @@ inline bool resident_rescale(PimManager *pim, const std::shared_ptr<Resident> &f
   return true;
 }
 
+/* the scheme's QHatInvModq (the table the caller passed in) against the one the cached plan derived from the moduli:
+ * a caller with other constants (another level's tables, a partial basis) stays on the CPU path */
+template <class IntVec>
+inline bool same_hat_inv(const CachedPlan<PimBasis> &plan, const IntVec &QHatInvModq, size_t sq, size_t sp) {
+  if (QHatInvModq.size() < sq) return false;
+  std::vector<uint64_t> hi(sq), hm(sq * sp);
+  if (fhe_basis_tables(plan.plan->handle(), hi.data(), hm.data()) != 0) return false;
+  for (size_t i = 0; i < sq; i++)
+    if (hi[i] != QHatInvModq[i].ConvertToInt()) return false;
+  return true;
+}
+
 /* DCRTPolyImpl::ApproxSwitchCRTBasis (dcrtpoly-impl.h:1034-1082): a over its first `sq` towers -> out over its own moduli */
-template <class Towers>
+template <class Towers, class IntVec>
 inline bool resident_approx_switch(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, size_t sq, const Towers &out,
-                                   std::shared_ptr<Resident> &rout) {
+                                   std::shared_ptr<Resident> &rout, const IntVec &QHatInvModq) {
   if (!pim || a.empty() || out.empty() || sq != a.size()) return false;      /* partial source bases stay on the CPU path */
   const int S = hook_stream(pim->context());
   auto da = ensure_device(pim, a, ra);
+  auto plan = basis_for(da->ring, ring_of(pim, out));
+  if (!same_hat_inv(plan, QHatInvModq, sq, out.size())) return false;
   auto r = new_resident(pim, out);
-  auto plan = basis_for(da->ring, r->ring);
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
     PimManager::check(fhe_approx_switch_crt_basis(plan.plan->handle(), r->d, da->d, 1, S), "pim hook: basis switch");
@@ -450,9 +463,9 @@ inline bool resident_approx_switch(PimManager *pim, const Towers &a, std::shared
 }
 
 /* DCRTPolyImpl::ApproxModDown (dcrtpoly-impl.h:1136-1175), EVALUATION input over QP: out over the first `sq` towers */
-template <class Towers>
+template <class Towers, class IntVec>
 inline bool resident_mod_down(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, size_t sq, uint64_t t,
-                              const Towers &out, std::shared_ptr<Resident> &rout) {
+                              const Towers &out, std::shared_ptr<Resident> &rout, const IntVec &PHatInvModp) {
   if (!pim || a.empty() || sq == 0 || sq >= a.size() || out.size() != sq) return false;
   const int S = hook_stream(pim->context());
   auto da = ensure_device(pim, a, ra);
@@ -469,6 +482,8 @@ inline bool resident_mod_down(PimManager *pim, const Towers &a, std::shared_ptr<
     rq = it->second.first;
     rp = it->second.second;
   }
+  auto plan = basis_for(rp, rq);
+  if (!same_hat_inv(plan, PHatInvModp, a.size() - sq, sq)) return false;
   auto r = std::make_shared<Resident>();
   r->ring = rq;
   r->ctx = pim->context();
@@ -477,7 +492,6 @@ inline bool resident_mod_down(PimManager *pim, const Towers &a, std::shared_ptr<
   r->n = da->n;
   PimManager::check(fhe_alloc(r->ctx, r->towers * r->n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
   r->device_newer = true;
-  auto plan = basis_for(rp, rq);
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
     PimManager::check(fhe_approx_mod_down(plan.plan->handle(), r->d, da->d, 1, t, S), "pim hook: mod down");
@@ -488,9 +502,9 @@ inline bool resident_mod_down(PimManager *pim, const Towers &a, std::shared_ptr<
 
 /* DCRTPolyImpl::ApproxModUp (dcrtpoly-impl.h:1085-1133): a over Q (either format) -> out over QP, EVALUATION.
  * `out` = host shells of the QP towers (moduli and roots only). */
-template <class Towers>
+template <class Towers, class IntVec>
 inline bool resident_mod_up(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
-                            std::shared_ptr<Resident> &rout, int format) {
+                            std::shared_ptr<Resident> &rout, int format, const IntVec &QHatInvModq) {
   if (!pim || a.empty() || out.size() <= a.size()) return false;
   const int S = hook_stream(pim->context());
   auto da = ensure_device(pim, a, ra);
@@ -507,6 +521,7 @@ inline bool resident_mod_up(PimManager *pim, const Towers &a, std::shared_ptr<Re
     rp = it->second;
   }
   auto plan = basis_for(da->ring, rp);
+  if (!same_hat_inv(plan, QHatInvModq, sq, sp)) return false;
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
     PimManager::check(fhe_approx_mod_up(plan.plan->handle(), r->d, da->d, 1, format, S), "pim hook: mod up");
@@ -531,18 +546,6 @@ inline bool resident_mod_reduce(PimManager *pim, const std::shared_ptr<Resident>
   }
   finish(r->ctx);
   res = r;
-  return true;
-}
-
-/* the scheme's QHatInvModq (the table the caller passed in) against the one the cached plan derived from the moduli:
- * a caller with other constants (another level's tables, a partial basis) stays on the CPU path */
-template <class IntVec>
-inline bool same_hat_inv(const CachedPlan<PimBasis> &plan, const IntVec &QHatInvModq, size_t sq, size_t sp) {
-  if (QHatInvModq.size() < sq) return false;
-  std::vector<uint64_t> hi(sq), hm(sq * sp);
-  if (fhe_basis_tables(plan.plan->handle(), hi.data(), hm.data()) != 0) return false;
-  for (size_t i = 0; i < sq; i++)
-    if (hi[i] != QHatInvModq[i].ConvertToInt()) return false;
   return true;
 }
 

@@ -215,7 +215,7 @@ def patch_impl(text):
                 "        std::vector<DCRTPolyImpl::PolyType> shell;\n"
                 "        for (const auto& tp : paramsQP->GetParams()) shell.emplace_back(tp, Format::EVALUATION, false);\n"
                 "        std::shared_ptr<pimhook::Resident> up;\n"
-                "        if (pimhook::resident_mod_up(pim.get(), m_vectors_, pimres_, shell, up, m_format == Format::EVALUATION ? 0 : 1)) {\n"
+                "        if (pimhook::resident_mod_up(pim.get(), m_vectors_, pimres_, shell, up, m_format == Format::EVALUATION ? 0 : 1, QHatInvModq)) {\n"
                 "            m_vectors_ = std::move(shell);\n"
                 "            pimres_    = up;\n"
                 "            m_format   = Format::EVALUATION;\n"
@@ -232,7 +232,7 @@ def patch_impl(text):
                 "    const std::vector<std::vector<NativeInteger>>& QHatModp, const std::vector<DoubleNativeInt>& modpBarrettMu) const {\n"
                 "    if (pim && m_vectors_.size() <= paramsQ->GetParams().size()) {\n"
                 "        DCRTPolyImpl<VecType> dev(paramsP, m_format, false);\n"
-                "        if (pimhook::resident_approx_switch(pim.get(), m_vectors_, pimres_, m_vectors_.size(), dev.m_vectors_, dev.pimres_)) {\n"
+                "        if (pimhook::resident_approx_switch(pim.get(), m_vectors_, pimres_, m_vectors_.size(), dev.m_vectors_, dev.pimres_, QHatInvModq)) {\n"
                 "            dev.pim = pim;\n"
                 "            return dev;\n"
                 "        }\n"
@@ -380,7 +380,7 @@ def patch_impl(text):
                 "        DCRTPolyImpl<VecType> dev(paramsQ, Format::EVALUATION, false);\n"
                 "        if (paramsQ->GetParams().size() > devQ)\n"
                 "            dev.DropLastElements(paramsQ->GetParams().size() - devQ);\n"
-                "        if (pimhook::resident_mod_down(pim.get(), m_vectors_, pimres_, devQ, t.ConvertToInt(), dev.m_vectors_, dev.pimres_)) {\n"
+                "        if (pimhook::resident_mod_down(pim.get(), m_vectors_, pimres_, devQ, t.ConvertToInt(), dev.m_vectors_, dev.pimres_, PHatInvModp)) {\n"
                 "            dev.pim = pim;\n"
                 "            return dev;\n"
                 "        }\n"

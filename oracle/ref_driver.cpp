@@ -264,6 +264,10 @@ static std::vector<NativeInteger> moduli_of(const ref_ctx* c) {
     for (auto& tp : c->params->GetParams()) m.push_back(tp->GetModulus());
     return m;
 }
+// test knob: a caller whose [ (Q/q_0)^-1 ]_{q_0} differs from the value the moduli imply (another level's table, say);
+// the device hooks must notice and leave such a call on the CPU path
+static int g_table_tweak = 0;
+void ref_set_table_tweak(int on) { g_table_tweak = on; }
 static ref_switch_tables make_switch_tables(const std::vector<NativeInteger>& mq, const std::vector<NativeInteger>& mp) {
     ref_switch_tables t;
     BigInteger Q(1);
@@ -273,6 +277,7 @@ static ref_switch_tables make_switch_tables(const std::vector<NativeInteger>& mq
     for (size_t i = 0; i < sq; i++) {
         BigInteger hat    = Q / BigInteger(mq[i]);
         t.hatInv[i]       = hat.ModInverse(BigInteger(mq[i])).ConvertToInt();
+        if (g_table_tweak && i == 0) t.hatInv[i] = t.hatInv[i].ModAdd(NativeInteger(1), mq[i]);
         t.hatInvPrecon[i] = t.hatInv[i].PrepModMulConst(mq[i]);
         t.hatModp[i].resize(sp);
         for (size_t j = 0; j < sp; j++) t.hatModp[i][j] = hat.Mod(BigInteger(mp[j])).ConvertToInt();

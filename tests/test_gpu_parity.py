@@ -434,6 +434,32 @@ def test_free_is_stream_ordered(pkg, backend, oracle):
     ring.close()
 
 
+def test_misaligned_polynomial_pointers_are_refused(pkg, backend, oracle):
+    """The polynomial kernels move 128-bit words: a pointer that is not 16-byte aligned is refused by the C ABI
+    (FHE_EINVAL) instead of reaching a kernel (fhe_b200.h, "Alignment"); the flat vector calls accept it."""
+    n, towers, batch = 1 << 10, 2, 1
+    q, psi = params(oracle, 60, n, towers)
+    ring = pkg.Ring(backend, n, q, psi)
+    blk = backend.alloc((ring.words(batch) + 2) * 8)
+    dst = backend.alloc((ring.words(batch) + 2) * 8)
+    odd, odd_dst = blk + 8, dst + 8
+    L = pkg._native.lib
+    for rc in (L.fhe_ntt_forward(ring.h, odd, batch, 0),
+               L.fhe_ntt_inverse(ring.h, odd, batch, 0),
+               L.fhe_automorphism(ring.h, odd_dst, blk, batch, 5, 0, 0),
+               L.fhe_automorphism(ring.h, dst, odd, batch, 5, 1, 0),
+               L.fhe_dcrt_op(ring.h, pkg.OP_MUL, dst, odd, blk, batch, 0)):
+        assert rc != 0
+        assert b"align" in L.fhe_last_error().lower() or b"misaligned" in L.fhe_last_error().lower()
+    x = np.arange(1, 102, dtype=np.uint64)
+    backend.h2d(odd, x)
+    backend.vec_op(pkg.OP_ADD, odd_dst, odd, odd, x.size, int(q[0]))
+    assert np.array_equal(backend.d2h(odd_dst, x.size), (x + x) % q[0])
+    backend.sync()
+    backend.free(blk); backend.free(dst)
+    ring.close()
+
+
 def test_flat_vector_eq_forms_in_place(pkg, backend, oracle):
     """VECTOR_EQ / SCALAR_EQ descriptor kinds run with dst == a (pim/common.h:14-21)."""
     q = 1152921504606748673

@@ -40,6 +40,7 @@ def load_hooked():
     H.ref_polys_binary.argtypes = [vp, vp, ci]
     H.ref_polys_approx_switch.restype = vp
     H.ref_polys_approx_switch.argtypes = [vp, vp]
+    H.ref_set_table_tweak.argtypes = [ctypes.c_int]
     H.ref_polys_approx_mod_down.restype = vp
     H.ref_polys_approx_mod_down.argtypes = [vp, vp, vp, u64]
     H.ref_polys_approx_mod_up.argtypes = [vp, vp, vp]
@@ -258,6 +259,65 @@ def test_resident_neighbouring_methods(hooked, oracle, pkg):
     for h in (ha, hb, h1, h2, hx, hs):
         H.ref_polys_free(h)
     for c in (cQ, cP, cQP, cRest):
+        H.ref_ctx_destroy(c)
+
+
+@pytest.mark.gpu
+def test_foreign_tables_stay_on_the_cpu_path(hooked, oracle, pkg):
+    """The device plans derive their constants from the moduli.  A caller that passes OTHER constants (here
+    [(Q/q_0)^-1]_{q_0} + 1) must get what the reference computes from ITS tables: ApproxSwitchCRTBasis, ApproxModUp
+    and ApproxModDown notice the difference and leave the call to the CPU statements (no launch), with or without
+    the handle the result is the same."""
+    H = hooked
+    n, sq, sp, batch = 1 << 10, 3, 2, 2
+    q, psi = oracle.gen_params(60, n, sq + sp)
+    mk = lambda a, b: H.ref_ctx_create(n, b - a, p(q[a:b].copy()), p(psi[a:b].copy()))
+    cQ, cP, cQP = mk(0, sq), mk(sq, sq + sp), mk(0, sq + sp)
+    x = oracle.fill_ring(batch, n, q[:sq].copy(), 81)
+    y = oracle.fill_ring(batch, n, q, 82)
+    ob = oracle.basis(n, q, psi, sq)
+
+    def run(attach):
+        out = []
+        hx = H.ref_polys_load(cQ, p(x), batch, 1)
+        if attach:
+            assert H.ref_polys_set_pim(hx, 1) == 0, H.ref_last_error()
+        hs = H.ref_polys_approx_switch(hx, cP)
+        r = np.empty((batch, sp, n), np.uint64)
+        H.ref_polys_store(hs, p(r))
+        out.append(r)
+        assert H.ref_polys_approx_mod_up(hx, cP, cQP) == 0, H.ref_last_error()
+        r = np.empty((batch, sq + sp, n), np.uint64)
+        H.ref_polys_store(hx, p(r))
+        out.append(r)
+        hy = H.ref_polys_load(cQP, p(y), batch, 0)
+        if attach:
+            assert H.ref_polys_set_pim(hy, 1) == 0
+        hd = H.ref_polys_approx_mod_down(hy, cQ, cP, 0)
+        r = np.empty((batch, sq, n), np.uint64)
+        H.ref_polys_store(hd, p(r))
+        out.append(r)
+        for h in (hx, hs, hy, hd):
+            H.ref_polys_free(h)
+        return out
+
+    H.ref_set_table_tweak(1)
+    try:
+        cpu = run(False)
+        launches0 = pkg._native.lib.fhe_launch_count()
+        dev = run(True)
+        launched = pkg._native.lib.fhe_launch_count() - launches0
+    finally:
+        H.ref_set_table_tweak(0)
+    for c, d in zip(cpu, dev):
+        assert np.array_equal(c, d)
+    assert not np.array_equal(cpu[0], ob.approx_switch(x)), "the tweak must change the result, else the test proves nothing"
+    # with the moduli's own tables the same calls do run on the device
+    launches1 = pkg._native.lib.fhe_launch_count()
+    good = run(True)
+    assert pkg._native.lib.fhe_launch_count() - launches1 > launched
+    assert np.array_equal(good[0], ob.approx_switch(x))
+    for c in (cQ, cP, cQP):
         H.ref_ctx_destroy(c)
 
 

@@ -22,6 +22,7 @@
 // N <= 256 (and any N <= 4096 on request) uses one CTA per tower entirely in shared memory.
 #include "ntt_steps.cuh"
 #include "kernels.h"
+#include <atomic>
 
 #include <algorithm>
 #include <cstdlib>
@@ -336,12 +337,16 @@ static int tile_log(int which) {
 template <int RL, int TL, bool INV>
 static cudaError_t launch_strided_t(const RingDev& r, u64* data, const u64* in, u32 outT, u32 inT, size_t batch, cudaStream_t st) {
     using K = StridedCfg<RL, TL>;
-    static bool attr_done = false;
-    if (!attr_done && K::SMEM > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(ntt_strided_kernel<RL, TL, INV>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
+    if (K::SMEM > 48 * 1024) {                         // a function attribute belongs to ONE device: remember it per device
+        static std::atomic<unsigned long long> attr_done{0};
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
         if (e != cudaSuccess) return e;
-        attr_done = true;
+        if (dev >= 64 || !((attr_done.load(std::memory_order_relaxed) >> dev) & 1)) {
+            e = cudaFuncSetAttribute(ntt_strided_kernel<RL, TL, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
+            if (e != cudaSuccess) return e;
+            if (dev < 64) attr_done.fetch_or(1ull << dev, std::memory_order_relaxed);
+        }
     }
     // batch items along y (and z beyond 32768 of them: the largest divisor of the batch that fits)
     unsigned by = (unsigned)batch, bz = 1;

@@ -206,7 +206,6 @@ struct fhe_ctx {
     std::map<int, Timer> timers;
     std::vector<void*> pinned;
     size_t chunk_bytes = 32ull << 20;   // host pipelines: bytes per operand per chunk (opts: chunk_mb)
-    int* d_err = nullptr;          // device flag written by kernels that can meet invalid elements
 };
 
 struct fhe_ring {
@@ -643,6 +642,7 @@ extern "C" int fhe_ntt_algo(fhe_ring* r, fhe_dptr x, size_t batch, int inverse, 
     if (!r->has_ntt) return fail(FHE_EINVAL, "fhe_ntt: ring was created without roots of unity");
     if (batch == 0) return FHE_OK;
     if (!x) return fail(FHE_EINVAL, "fhe_ntt: null device pointer");
+    if (r->dev.N > 1 && (x & 15)) return fail(FHE_EINVAL, "fhe_ntt: device pointers must be 16-byte aligned");
     if (r->dev.N == 1) return FHE_OK;
     CUDA_TRY(launch_ntt(r->dev, (uint64_t*)(uintptr_t)x, batch, inverse != 0, s, algo));
     return FHE_OK;
@@ -667,6 +667,7 @@ extern "C" int fhe_automorphism(fhe_ring* r, fhe_dptr dst, fhe_dptr src, size_t 
     if (k % 2 == 0) return fail(FHE_EINVAL, "Automorphism index not odd");          // poly-impl.h:346-347
     if (batch == 0) return FHE_OK;
     if (!dst || !src) return fail(FHE_EINVAL, "fhe_automorphism: null device pointer");
+    if (r->dev.N > 1 && ((dst | src) & 15)) return fail(FHE_EINVAL, "fhe_automorphism: device pointers must be 16-byte aligned");
     if (dst == src) return fail(FHE_EINVAL, "fhe_automorphism: dst must not alias src (it is a permutation)");
     CUDA_TRY(launch_automorphism(r->dev, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, batch, k, format, s));
     return FHE_OK;
@@ -691,6 +692,7 @@ extern "C" int fhe_automorphism_map(fhe_ring* r, fhe_dptr dst, fhe_dptr src, siz
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
     if (!dst || !src || !map) return fail(FHE_EINVAL, "fhe_automorphism_map: null device pointer");
+    if (r->dev.N > 1 && ((dst | src) & 15)) return fail(FHE_EINVAL, "fhe_automorphism_map: device pointers must be 16-byte aligned");
     if (dst == src) return fail(FHE_EINVAL, "fhe_automorphism_map: dst must not alias src");
     CUDA_TRY(launch_automorphism_map(r->dev, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, batch,
                                      (const uint32_t*)(uintptr_t)map, s));
@@ -784,22 +786,19 @@ extern "C" int fhe_vec_modop(fhe_ctx* ctx, int kind, fhe_dptr dst, fhe_dptr src,
     if ((kind == MODEXP || kind == MODEXPEQ) && p >= mod) p %= mod;
     CUDA_TRY(cudaSetDevice(ctx->device));
     bool inv = kind == MODINVERSE || kind == MODINVERSEEQ;
-    if (inv) {
-        std::lock_guard<std::mutex> lk(ctx->mu);
-        if (!ctx->d_err) {
-            void* e = nullptr;
-            if ((rc = ctx->arena.alloc(256, &e))) return rc;
-            ctx->d_err = (int*)e;
-        }
-    }
-    if (inv) CUDA_TRY(cudaMemsetAsync(ctx->d_err, 0, sizeof(int), s));
-    CUDA_TRY(launch_modop(kind, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, n, mod, p, q, ctx->d_err, s));
+    void* err = nullptr;                         // the error word is this call's own: two threads may invert at once
+    if (inv && (rc = ctx->arena.alloc(256, &err))) return rc;
+    cudaError_t e = inv ? cudaMemsetAsync(err, 0, sizeof(int), s) : cudaSuccess;
+    if (e == cudaSuccess)
+        e = launch_modop(kind, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, n, mod, p, q, (int*)err, s);
+    int flag = 0;
     if (inv) {                                   // the reference throws math_error: report it synchronously
-        int flag = 0;
-        CUDA_TRY(cudaMemcpyAsync(&flag, ctx->d_err, sizeof(int), cudaMemcpyDeviceToHost, s));
-        CUDA_TRY(cudaStreamSynchronize(s));
-        if (flag) return fail(FHE_EINVAL, "fhe_vec_modop: an element does not have a ModInverse using %llu", (unsigned long long)mod);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&flag, err, sizeof(int), cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        arena_park(ctx, err);
     }
+    if (e != cudaSuccess) return fail(FHE_ECUDA, "fhe_vec_modop: %s", cudaGetErrorString(e));
+    if (flag) return fail(FHE_EINVAL, "fhe_vec_modop: an element does not have a ModInverse using %llu", (unsigned long long)mod);
     return FHE_OK;
 }
 
@@ -1088,6 +1087,7 @@ extern "C" int fhe_approx_switch_crt_basis(fhe_basis* b, fhe_dptr dst, fhe_dptr 
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
     if (!dst || !src) return fail(FHE_EINVAL, "fhe_approx_switch_crt_basis: null device pointer");
+    if ((dst | src) & 15) return fail(FHE_EINVAL, "fhe_approx_switch_crt_basis: device pointers must be 16-byte aligned");
     CUDA_TRY(launch_basis_switch(b->dev, (uint64_t*)(uintptr_t)dst, b->dev.sp, 0, (const uint64_t*)(uintptr_t)src, b->dev.sq, 0,
                                  batch, b->from->dev.logN, false, s));
     return FHE_OK;
@@ -1127,6 +1127,7 @@ extern "C" int fhe_approx_mod_up(fhe_basis* b, fhe_dptr dst_qp, fhe_dptr src_q, 
     if (format != 0 && format != 1) return fail(FHE_EINVAL, "fhe_approx_mod_up: format must be 0 or 1");
     if (batch == 0) return FHE_OK;
     if (!dst_qp || !src_q) return fail(FHE_EINVAL, "fhe_approx_mod_up: null device pointer");
+    if ((dst_qp | src_q) & 15) return fail(FHE_EINVAL, "fhe_approx_mod_up: device pointers must be 16-byte aligned");
     const uint32_t N = b->from->dev.N, logN = b->from->dev.logN, sq = b->dev.sq, sp = b->dev.sp;
     uint64_t* dst = (uint64_t*)(uintptr_t)dst_qp;
     const uint64_t* src = (const uint64_t*)(uintptr_t)src_q;
@@ -1156,6 +1157,7 @@ extern "C" int fhe_approx_mod_down(fhe_basis* b, fhe_dptr dst_q, fhe_dptr src_qp
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
     if (!dst_q || !src_qp) return fail(FHE_EINVAL, "fhe_approx_mod_down: null device pointer");
+    if ((dst_q | src_qp) & 15) return fail(FHE_EINVAL, "fhe_approx_mod_down: device pointers must be 16-byte aligned");
     fhe_ring *P = b->from, *Q = b->to;                      // the basis switches P -> Q
     const uint32_t N = P->dev.N, logN = P->dev.logN, sp = b->dev.sq, sq = b->dev.sp;
     if (!b->pinv_ready) {                                    // [P^-1]_{q_i}, rns-cryptoparameters.cpp:190-197
@@ -1278,6 +1280,7 @@ static int rescale_run(fhe_rescale* p, fhe_dptr dst_, fhe_dptr src_, size_t batc
     if (format != 0 && format != 1) return fail(FHE_EINVAL, "%s: format must be 0 or 1", who);
     if (batch == 0) return FHE_OK;
     if (!dst_ || !src_) return fail(FHE_EINVAL, "%s: null device pointer", who);
+    if ((dst_ | src_) & 15) return fail(FHE_EINVAL, "%s: device pointers must be 16-byte aligned", who);
     const uint32_t N = p->ring->dev.N, logN = p->ring->dev.logN, T = p->ring->dev.T, l = T - 1;
     const uint64_t ql = p->ring->q[l];
     uint64_t* dst = (uint64_t*)(uintptr_t)dst_;
@@ -1349,6 +1352,7 @@ extern "C" int fhe_switch_crt_basis(fhe_basis* b, fhe_dptr dst, fhe_dptr src, si
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
     if (!dst || !src) return fail(FHE_EINVAL, "fhe_switch_crt_basis: null device pointer");
+    if ((dst | src) & 15) return fail(FHE_EINVAL, "fhe_switch_crt_basis: device pointers must be 16-byte aligned");
     if ((rc = basis_exact_ready(b))) return rc;
     CUDA_TRY(launch_basis_switch(b->dev, (uint64_t*)(uintptr_t)dst, b->dev.sp, 0, (const uint64_t*)(uintptr_t)src, b->dev.sq, 0,
                                  batch, b->from->dev.logN, true, s));
@@ -1366,6 +1370,7 @@ static int expand_run(fhe_basis* b, fhe_dptr dst_, fhe_dptr src_q, size_t batch,
         return fail(FHE_EINVAL, "%s: formats must be 0 or 1", who);
     if (batch == 0) return FHE_OK;
     if (!dst_ || !src_q) return fail(FHE_EINVAL, "%s: null device pointer", who);
+    if ((dst_ | src_q) & 15) return fail(FHE_EINVAL, "%s: device pointers must be 16-byte aligned", who);
     if ((rc = basis_exact_ready(b))) return rc;
     const uint32_t N = b->from->dev.N, logN = b->from->dev.logN, sq = b->dev.sq, sp = b->dev.sp;
     const uint32_t q0 = reverse ? sp : 0, p0 = reverse ? 0 : sq;                               // first tower of each part
@@ -1414,6 +1419,7 @@ extern "C" int fhe_fast_expand_crt_basis_pl_over_q(fhe_basis* q2pl, fhe_basis* p
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
     if (!dst_qlpl || !src_q) return fail(FHE_EINVAL, "%s: null device pointer", who);
+    if ((dst_qlpl | src_q) & 15) return fail(FHE_EINVAL, "%s: device pointers must be 16-byte aligned", who);
     if (dst_qlpl == src_q) return fail(FHE_EINVAL, "%s: dst must not be src (different tower counts)", who);
     if (pl2ql->to->dev.T != q2pl->dev.sp) return fail(FHE_EINVAL, "%s: Ql and Pl must have the same number of towers", who);
     if ((rc = basis_exact_ready(pl2ql))) return rc;
@@ -1470,6 +1476,7 @@ static int tower_scale_run(fhe_tower_scale* p, int mode, uint32_t sl, fhe_dptr d
     if (mode == 0 && (sl == 0 || sl > T)) return fail(FHE_EINVAL, "%s: size_ql must be in [1, %u]", who, T);
     if (batch == 0) return FHE_OK;
     if (!dst || !src) return fail(FHE_EINVAL, "%s: null device pointer", who);
+    if ((dst | src) & 15) return fail(FHE_EINVAL, "%s: device pointers must be 16-byte aligned", who);
     if (dst == src && !(mode == 0 && sl == T))
         return fail(FHE_EINVAL, "%s: dst must not be src (different tower counts)", who);
     CUDA_TRY(launch_tower_scale(mode, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, batch, p->ring->dev.logN, sl, T,
@@ -1548,6 +1555,7 @@ extern "C" int fhe_scale_and_round(fhe_scale_round* p, fhe_dptr dst, fhe_dptr sr
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
     if (!dst || !src) return fail(FHE_EINVAL, "fhe_scale_and_round: null device pointer");
+    if ((dst | src) & 15) return fail(FHE_EINVAL, "fhe_scale_and_round: device pointers must be 16-byte aligned");
     CUDA_TRY(launch_scale_round(p->dev, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, batch, p->ring->dev.logN, s));
     return FHE_OK;
 }
@@ -1930,6 +1938,7 @@ extern "C" int fhe_scale_and_round_native(fhe_decrypt_scale* p, fhe_dptr dst, fh
     if (rc) return rc;
     if (batch == 0) return FHE_OK;
     if (!dst || !src) return fail(FHE_EINVAL, "fhe_scale_and_round_native: null device pointer");
+    if ((dst | src) & 15) return fail(FHE_EINVAL, "fhe_scale_and_round_native: device pointers must be 16-byte aligned");
     CUDA_TRY(launch_decrypt_scale(p->dev, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src, batch, p->ring->dev.logN, s));
     return FHE_OK;
 }
