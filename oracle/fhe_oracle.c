@@ -1049,3 +1049,248 @@ void orc_fill_uniform(uint64_t* x, size_t n, uint64_t q, uint64_t seed, uint64_t
 #pragma omp parallel for schedule(static)
     for (long i = 0; i < (long)n; i++) x[i] = orc_uniform_at(seed, first_index + (uint64_t)i, q);
 }
+
+/* ---- BEHZ: the BFV multiplication technique of Bajard-Eynard-Hasan-Zucca ----------------------------------
+ * DCRTPolyImpl::FastBaseConvqToBskMontgomery (dcrtpoly-impl.h:2069-2209), FastRNSFloorq (:2212-2271),
+ * FastBaseConvSK (:2309-2420) and the decryption ScaleAndRound(moduliQ, t, tgamma, ...) (:2005-2050), with the
+ * tables of CryptoParametersBFVRNS::PrecomputeCRTTables (src/pke/lib/scheme/bfvrns/bfvrns-cryptoparameters.cpp:
+ * 662-885) restated in word arithmetic.  The ring is Q followed by Bsk = B u {msk}: nq towers of Q, nb = |B| + 1
+ * towers of Bsk, the last one msk.  mtilde = 2^16 and gamma = 2^26 are the scheme's constants
+ * (bfvrns-cryptoparameters.h: m_mtilde, m_gamma). */
+#define BEHZ_TABLES 17
+struct orc_behz {
+    orc_ctx *Q, *Bsk;
+    uint32_t N, nq, nb;
+    uint64_t t;
+    uint64_t* tab[BEHZ_TABLES];
+    size_t len[BEHZ_TABLES];
+};
+
+static uint64_t prod_except(const uint64_t* f, uint32_t n, uint32_t skip, uint64_t m) {
+    uint64_t r = 1 % m;
+    for (uint32_t k = 0; k < n; k++) if (k != skip) r = mulmod_u128(r, f[k] % m, m);
+    return r;
+}
+static uint64_t* behz_new(orc_behz* z, int which, size_t n) {
+    z->tab[which] = (uint64_t*)calloc(n ? n : 1, 8);
+    z->len[which] = n;
+    return z->tab[which];
+}
+
+orc_behz* orc_behz_create(const orc_ctx* QBsk, uint32_t nq, uint64_t t) {
+    if (!QBsk || nq == 0 || QBsk->T < nq + 2 || t < 2) return NULL;
+    orc_behz* z = (orc_behz*)calloc(1, sizeof(orc_behz));
+    const uint32_t nb = QBsk->T - nq, nB = nb - 1, NONE = 0xffffffffu;
+    const uint64_t* q = QBsk->q;
+    const uint64_t* bsk = QBsk->q + nq;
+    const uint64_t msk = bsk[nB], mtilde = (uint64_t)1 << 16, gamma = (uint64_t)1 << 26;
+    z->N = QBsk->N; z->nq = nq; z->nb = nb; z->t = t;
+    z->Q = orc_ctx_create(QBsk->N, nq, q, QBsk->psi);
+    z->Bsk = orc_ctx_create(QBsk->N, nb, bsk, QBsk->psi + nq);
+    uint64_t* hatinv = (uint64_t*)malloc(8 * nq);                       /* [(Q/q_i)^-1]_{q_i} */
+    for (uint32_t i = 0; i < nq; i++) hatinv[i] = orc_modinv(prod_except(q, nq, i, q[i]), q[i]);
+    uint64_t* T0 = behz_new(z, 0, nq);                                  /* [mtilde*(Q/q_i)^-1]_{q_i}           :763-776 */
+    uint64_t* T1 = behz_new(z, 1, (size_t)nq * nb);                     /* [Q/q_i]_{bsk_j}                     :737-750 */
+    uint64_t* T2 = behz_new(z, 2, nq);                                  /* [Q/q_i]_{mtilde}                    :749 */
+    uint64_t* T6 = behz_new(z, 6, nq);                                  /* [t*(Q/q_i)^-1]_{q_i}                :724-735 */
+    uint64_t* T7 = behz_new(z, 7, (size_t)nq * nb);                     /* [q_i^-1]_{bsk_j}                    :752-758 */
+    for (uint32_t i = 0; i < nq; i++) {
+        T0[i] = mulmod_u128(hatinv[i], mtilde % q[i], q[i]);
+        T6[i] = mulmod_u128(hatinv[i], t % q[i], q[i]);
+        T2[i] = prod_except(q, nq, i, mtilde);
+        for (uint32_t j = 0; j < nb; j++) {
+            T1[(size_t)i * nb + j] = prod_except(q, nq, i, bsk[j]);
+            T7[(size_t)i * nb + j] = orc_modinv(q[i] % bsk[j], bsk[j]);
+        }
+    }
+    uint64_t* T3 = behz_new(z, 3, nb);                                  /* [Q]_{bsk_j}                         :783-791 */
+    uint64_t* T5 = behz_new(z, 5, nb);                                  /* [mtilde^-1]_{bsk_j}                 :793-802 */
+    uint64_t* T8 = behz_new(z, 8, nb);                                  /* [t*Q^-1]_{bsk_j}                    :804-813 */
+    for (uint32_t j = 0; j < nb; j++) {
+        T3[j] = prod_except(q, nq, NONE, bsk[j]);
+        T5[j] = orc_modinv(mtilde % bsk[j], bsk[j]);
+        T8[j] = mulmod_u128(orc_modinv(T3[j], bsk[j]), t % bsk[j], bsk[j]);
+    }
+    uint64_t* T4 = behz_new(z, 4, 1);                                   /* [-Q^-1]_{mtilde}                    :778-781 */
+    T4[0] = mulmod_u128(mtilde - 1, orc_modinv(prod_except(q, nq, NONE, mtilde), mtilde), mtilde);
+    uint64_t* T9 = behz_new(z, 9, nB);                                  /* [(B/b_i)^-1]_{b_i}                  :815-827 */
+    uint64_t* T10 = behz_new(z, 10, (size_t)nB * nq);                   /* [B/b_i]_{q_j}                       :829-839 */
+    uint64_t* T11 = behz_new(z, 11, nB);                                /* [B/b_i]_{msk}                       :841-846 */
+    for (uint32_t i = 0; i < nB; i++) {
+        T9[i] = orc_modinv(prod_except(bsk, nB, i, bsk[i]), bsk[i]);
+        T11[i] = prod_except(bsk, nB, i, msk);
+        for (uint32_t j = 0; j < nq; j++) T10[(size_t)i * nq + j] = prod_except(bsk, nB, i, q[j]);
+    }
+    uint64_t* T12 = behz_new(z, 12, 1);                                 /* [B^-1]_{msk}                        :848-850 */
+    T12[0] = orc_modinv(prod_except(bsk, nB, NONE, msk), msk);
+    uint64_t* T13 = behz_new(z, 13, nq);                                /* [B]_{q_i}                           :852-858 */
+    for (uint32_t i = 0; i < nq; i++) T13[i] = prod_except(bsk, nB, NONE, q[i]);
+    const uint64_t tgamma = t * gamma;                                  /* :862-864 */
+    uint64_t* T14 = behz_new(z, 14, 1);
+    T14[0] = tgamma;
+    uint64_t* T15 = behz_new(z, 15, nq);                                /* [-q_i^-1]_{t*gamma}                 :866-876 */
+    uint64_t* T16 = behz_new(z, 16, nq);                                /* [t*gamma*(Q/q_i)^-1]_{q_i}          :878-891 */
+    for (uint32_t i = 0; i < nq; i++) {
+        T15[i] = mulmod_u128(tgamma - 1, orc_modinv(q[i] % tgamma, tgamma), tgamma);
+        T16[i] = mulmod_u128(mulmod_u128(hatinv[i], gamma % q[i], q[i]), t % q[i], q[i]);
+    }
+    free(hatinv);
+    return z;
+}
+
+void orc_behz_destroy(orc_behz* z) {
+    if (!z) return;
+    for (int k = 0; k < BEHZ_TABLES; k++) free(z->tab[k]);
+    orc_ctx_destroy(z->Q); orc_ctx_destroy(z->Bsk);
+    free(z);
+}
+
+/* copies table `which` (numbering above) to out when out is not NULL; returns its length in words */
+size_t orc_behz_table(const orc_behz* z, int which, uint64_t* out) {
+    if (!z || which < 0 || which >= BEHZ_TABLES) return 0;
+    if (out) memcpy(out, z->tab[which], 8 * z->len[which]);
+    return z->len[which];
+}
+
+/* FastBaseConvqToBskMontgomery (dcrtpoly-impl.h:2069-2209): in over Q [B][nq][N] in `format` (0 EVALUATION,
+ * 1 COEFFICIENT) -> out over QBsk [B][nq+nb][N], EVALUATION */
+void orc_behz_q_to_bsk_montgomery(const orc_behz* z, uint64_t* out, const uint64_t* in, size_t B, int format) {
+    const uint32_t N = z->N, nq = z->nq, nb = z->nb, T = nq + nb;
+    const uint64_t* q = z->Q->q;
+    const uint64_t* bsk = z->Bsk->q;
+    const uint64_t mtilde = (uint64_t)1 << 16, mtilde_half = mtilde >> 1, mtilde_minus_1 = mtilde - 1;
+    size_t wq = B * nq * (size_t)N, wb = B * nb * (size_t)N;
+    uint64_t* coef = (uint64_t*)malloc(wq * 8);
+    uint64_t* part = (uint64_t*)malloc(wb * 8);
+    memcpy(coef, in, wq * 8);
+    if (format == 0) orc_dcrt_ntt(z->Q, 1, coef, B, 0);                  /* :2087-2090 */
+    /* step 0, mod Bsk (:2103-2127): the twist by [mtilde*(Q/q_i)^-1]_{q_i} and the 128-bit sums are
+     * ApproxSwitchCRTBasis's own statements with these two tables */
+    orc_approx_switch(part, coef, B, N, q, nq, bsk, nb, z->tab[0], z->tab[1]);
+    uint64_t* pre0 = (uint64_t*)malloc(8 * nq);
+    uint64_t *preQ = (uint64_t*)malloc(8 * nb), *preI = (uint64_t*)malloc(8 * nb);
+    for (uint32_t i = 0; i < nq; i++) pre0[i] = orc_prep_mulconst(z->tab[0][i], q[i]);
+    for (uint32_t j = 0; j < nb; j++) {
+        preQ[j] = orc_prep_mulconst(z->tab[3][j], bsk[j]);
+        preI[j] = orc_prep_mulconst(z->tab[5][j], bsk[j]);
+    }
+    long items = (long)(B * N);
+#pragma omp parallel for schedule(static)
+    for (long e = 0; e < items; e++) {
+        size_t b = (size_t)e / N, k = (size_t)e % N;
+        uint64_t r = 0;                                                  /* mod mtilde = 2^16 (:2148-2160) */
+        for (uint32_t i = 0; i < nq; i++)
+            r += orc_modmul_const(coef[(b * nq + i) * N + k], z->tab[0][i], q[i], pre0[i]) * z->tab[2][i];
+        r &= mtilde_minus_1;
+        r *= z->tab[4][0];                                               /* step 1 (:2168-2171) */
+        r &= mtilde_minus_1;
+        for (uint32_t j = 0; j < nb; j++) {                              /* :2173-2190 */
+            uint64_t rm = r;
+            if (r >= mtilde_half) rm += bsk[j] - mtilde;
+            rm = orc_modmul_const(rm, z->tab[3][j], bsk[j], preQ[j]);
+            uint64_t* c = part + (b * nb + j) * N + k;
+            rm = orc_modadd_fast(rm, *c, bsk[j]);
+            *c = orc_modmul_const(rm, z->tab[5][j], bsk[j], preI[j]);
+        }
+    }
+    if (format == 0) {                                                   /* :2194-2197 the stored EVALUATION towers */
+        towers_copy(out, T, 0, in, nq, 0, nq, B, N);
+    } else {                                                             /* :2198-2202 */
+        orc_dcrt_ntt(z->Q, 0, coef, B, 0);
+        towers_copy(out, T, 0, coef, nq, 0, nq, B, N);
+    }
+    orc_dcrt_ntt(z->Bsk, 0, part, B, 0);                                 /* :2204-2206 */
+    towers_copy(out, T, nq, part, nb, 0, nb, B, N);
+    free(coef); free(part); free(pre0); free(preQ); free(preI);
+}
+
+/* FastRNSFloorq (dcrtpoly-impl.h:2212-2271), in place on x over QBsk [B][nq+nb][N]: the towers of Q are left
+ * multiplied by [t*(Q/q_i)^-1]_{q_i} (:2233-2243), the towers of Bsk hold the result */
+void orc_behz_fast_rns_floor_q(const orc_behz* z, uint64_t* x, size_t B) {
+    const uint32_t N = z->N, nq = z->nq, nb = z->nb, T = nq + nb;
+    const uint64_t* q = z->Q->q;
+    const uint64_t* bsk = z->Bsk->q;
+    size_t wq = B * nq * (size_t)N, wb = B * nb * (size_t)N;
+    uint64_t* xq = (uint64_t*)calloc(wq, 8);
+    uint64_t* conv = (uint64_t*)malloc(wb * 8);
+    towers_copy(xq, nq, 0, x, T, 0, nq, B, N);
+    /* :2245-2256 = ApproxSwitchCRTBasis's statements with [t*(Q/q_i)^-1]_{q_i} and [q_i^-1]_{bsk_j} */
+    orc_approx_switch(conv, xq, B, N, q, nq, bsk, nb, z->tab[6], z->tab[7]);
+    for (size_t b = 0; b < B; b++) {
+        for (uint32_t i = 0; i < nq; i++) {
+            uint64_t pre = orc_prep_mulconst(z->tab[6][i], q[i]);
+            uint64_t* v = x + (b * T + i) * N;
+            for (uint32_t k = 0; k < N; k++) v[k] = orc_modmul_const(v[k], z->tab[6][i], q[i], pre);
+        }
+        for (uint32_t j = 0; j < nb; j++) {                              /* :2260-2269 */
+            uint64_t pre = orc_prep_mulconst(z->tab[8][j], bsk[j]);
+            uint64_t* v = x + (b * T + nq + j) * N;
+            const uint64_t* c = conv + (b * nb + j) * N;
+            for (uint32_t k = 0; k < N; k++)
+                v[k] = orc_modsub_fast(orc_modmul_const(v[k], z->tab[8][j], bsk[j], pre), c[k], bsk[j]);
+        }
+    }
+    free(xq); free(conv);
+}
+
+/* FastBaseConvSK (dcrtpoly-impl.h:2309-2420): in over QBsk [B][nq+nb][N] (only the towers of Bsk are read) ->
+ * out over Q [B][nq][N] */
+void orc_behz_fast_base_conv_sk(const orc_behz* z, uint64_t* out, const uint64_t* in, size_t B) {
+    const uint32_t N = z->N, nq = z->nq, nb = z->nb, nB = nb - 1, T = nq + nb;
+    const uint64_t* q = z->Q->q;
+    const uint64_t* bsk = z->Bsk->q;
+    const uint64_t msk = bsk[nB], mskDivTwo = msk / 2;
+    size_t wB = B * nB * (size_t)N;
+    uint64_t* xb = (uint64_t*)calloc(wB, 8);
+    uint64_t* alpha = (uint64_t*)malloc(B * (size_t)N * 8);
+    towers_copy(xb, nB, 0, in, T, nq, nB, B, N);
+    /* FastBaseconv(x, B, q) (:2327-2349) and FastBaseConv(x, B, msk) (:2351-2364): ApproxSwitchCRTBasis's statements
+     * with [(B/b_i)^-1]_{b_i} and [B/b_i]_{q_j} / [B/b_i]_{msk} */
+    orc_approx_switch(out, xb, B, N, bsk, nB, q, nq, z->tab[9], z->tab[10]);
+    orc_approx_switch(alpha, xb, B, N, bsk, nB, &msk, 1, z->tab[9], z->tab[11]);
+    const uint64_t binv = z->tab[12][0], binvp = orc_prep_mulconst(binv, msk);
+    for (size_t b = 0; b < B; b++) {
+        const uint64_t* xsk = in + (b * T + nq + nB) * N;
+        uint64_t* a = alpha + b * N;
+        for (uint32_t k = 0; k < N; k++)                                 /* :2366-2371 */
+            a[k] = orc_modmul_const(orc_modsub_fast(a[k], xsk[k], msk), binv, msk, binvp);
+        for (uint32_t i = 0; i < nq; i++) {                              /* :2373-2388 */
+            uint64_t pre = orc_prep_mulconst(z->tab[13][i], q[i]);
+            uint64_t* o = out + (b * nq + i) * N;
+            for (uint32_t k = 0; k < N; k++) {
+                uint64_t ab = a[k];
+                if (ab > mskDivTwo) ab = orc_modsub_fast(ab, msk, q[i]);
+                ab = orc_modmul_const(ab, z->tab[13][i], q[i], pre);
+                o[k] = orc_modsub_fast(o[k], ab, q[i]);
+            }
+        }
+    }
+    free(xb); free(alpha);
+}
+
+/* ScaleAndRound(moduliQ, t, tgamma, tgammaQHatModq, .., negInvqModtgamma, ..) -> NativePoly
+ * (dcrtpoly-impl.h:2005-2050): in over Q [B][nq][N], COEFFICIENT -> out [B][N] */
+void orc_behz_scale_and_round(const orc_behz* z, uint64_t* out, const uint64_t* in, size_t B) {
+    const uint32_t N = z->N, nq = z->nq;
+    const uint64_t* q = z->Q->q;
+    const uint64_t tgamma = z->tab[14][0], gammaMinus1 = (1 << 26) - 1;
+    uint64_t *p1 = (uint64_t*)malloc(8 * nq), *p2 = (uint64_t*)malloc(8 * nq);
+    for (uint32_t i = 0; i < nq; i++) {
+        p1[i] = orc_prep_mulconst(z->tab[16][i], q[i]);
+        p2[i] = orc_prep_mulconst(z->tab[15][i], tgamma);
+    }
+    long items = (long)(B * N);
+#pragma omp parallel for schedule(static)
+    for (long e = 0; e < items; e++) {
+        size_t b = (size_t)e / N, k = (size_t)e % N;
+        uint64_t s = 0;
+        for (uint32_t i = 0; i < nq; i++) {
+            uint64_t tmp = orc_modmul_const(in[(b * nq + i) * N + k], z->tab[16][i], q[i], p1[i]);
+            tmp = orc_modmul_const(tmp, z->tab[15][i], tgamma, p2[i]);
+            s = orc_modadd_fast(s, tmp, tgamma);
+        }
+        s += s & gammaMinus1;
+        out[e] = s >> 26;
+    }
+    free(p1); free(p2);
+}

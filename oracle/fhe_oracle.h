@@ -89,6 +89,19 @@ void     orc_keyswitch_inner(const orc_ctx* QlP, uint32_t np, uint64_t* c0, uint
                              const uint64_t* evk_b, const uint64_t* evk_a, size_t B);
 void     orc_keyswitch_hybrid(const orc_ctx* QlP, uint32_t sizeQl, uint32_t alpha, uint64_t* ct0, uint64_t* ct1, const uint64_t* c,
                               const uint64_t* evk_b, const uint64_t* evk_a, size_t B, uint64_t t);
+/* BEHZ (dcrtpoly-impl.h:2005-2050, 2069-2420; tables of bfvrns-cryptoparameters.cpp:662-885).  QBsk = nq towers of Q
+ * followed by Bsk = B u {msk}.  Tables by number: 0 mtildeQHatInvModq[nq], 1 QHatModbsk[nq][nb], 2 QHatModmtilde[nq],
+ * 3 QModbsk[nb], 4 negQInvModmtilde, 5 mtildeInvModbsk[nb], 6 tQHatInvModq[nq], 7 qInvModbsk[nq][nb], 8 tQInvModbsk[nb],
+ * 9 BHatInvModb[nb-1], 10 BHatModq[nb-1][nq], 11 BHatModmsk[nb-1], 12 BInvModmsk, 13 BModq[nq], 14 tgamma,
+ * 15 negInvqModtgamma[nq], 16 tgammaQHatInvModq[nq] */
+typedef struct orc_behz orc_behz;
+orc_behz* orc_behz_create(const orc_ctx* QBsk, uint32_t nq, uint64_t t);
+void     orc_behz_destroy(orc_behz* z);
+size_t   orc_behz_table(const orc_behz* z, int which, uint64_t* out);
+void     orc_behz_q_to_bsk_montgomery(const orc_behz* z, uint64_t* out_qbsk, const uint64_t* in_q, size_t B, int format);
+void     orc_behz_fast_rns_floor_q(const orc_behz* z, uint64_t* x_qbsk, size_t B);
+void     orc_behz_fast_base_conv_sk(const orc_behz* z, uint64_t* out_q, const uint64_t* in_qbsk, size_t B);
+void     orc_behz_scale_and_round(const orc_behz* z, uint64_t* out, const uint64_t* in_q, size_t B);
 int      orc_max_threads(void);
 
 /* ---- automorphism X -> X^k, k odd ----

@@ -13,6 +13,7 @@
 #include "utils/serial.h"
 
 #include <chrono>
+#include <functional>
 #include <cstdint>
 #include <cstring>
 #include <memory>
@@ -1060,5 +1061,193 @@ int ref_max_threads(void) { return omp_get_max_threads(); }
 // OpenFHE caps its tower loops at the value omp_get_max_threads() had when the library was loaded
 // (ParallelControls::machineThreads, utils/parallel.h:52), so OMP_NUM_THREADS must also be right at load time.
 void ref_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+
+// ---- BEHZ: FastBaseConvqToBskMontgomery / FastRNSFloorq / FastBaseConvSK / ScaleAndRound(moduliQ, t, tgamma, ...) ----
+// The tables are the ones CryptoParametersBFVRNS::PrecomputeCRTTables builds for multTech == BEHZ
+// (src/pke/lib/scheme/bfvrns/bfvrns-cryptoparameters.cpp:662-885; the pke library is not part of this build), computed
+// here with the reference's BigInteger from the same definitions; mtilde = 2^16, gamma = 2^26
+// (src/pke/include/scheme/bfvrns/bfvrns-cryptoparameters.h).  QBsk = Q followed by B and msk.
+struct ref_behz {
+    ref_ctx* QBsk;
+    std::shared_ptr<ILDCRTParams<BigInteger>> paramsQ;
+    uint32_t nq, nb;
+    NativeInteger t, tgamma, BInvModmsk, BInvModmskPrecon;
+    uint64_t negQInvModmtilde;
+    std::vector<NativeInteger> moduliQ, moduliBsk;
+    std::vector<DoubleNativeInt> modqMu, modbskMu;
+    std::vector<NativeInteger> mtildeQHatInvModq, mtildeQHatInvModqPrecon, QModbsk, QModbskPrecon, mtildeInvModbsk,
+        mtildeInvModbskPrecon, tQHatInvModq, tQHatInvModqPrecon, tQInvModbsk, tQInvModbskPrecon, BHatInvModb, BHatInvModbPrecon,
+        BHatModmsk, BModq, BModqPrecon, negInvqModtgamma, negInvqModtgammaPrecon, tgammaQHatInvModq, tgammaQHatInvModqPrecon;
+    std::vector<std::vector<NativeInteger>> QHatModbsk, qInvModbsk, BHatModq;
+    std::vector<uint64_t> QHatModmtilde;
+};
+static std::vector<DoubleNativeInt> barrett_mu_128(const std::vector<NativeInteger>& m) {
+    const BigInteger B128("340282366920938463463374607431768211456"), T64("18446744073709551616");
+    std::vector<DoubleNativeInt> mu(m.size());
+    for (size_t j = 0; j < m.size(); j++) {
+        BigInteger v = B128 / BigInteger(m[j]);
+        uint64_t val[2] = {(v % T64).ConvertToInt(), v.RShift(64).ConvertToInt()};
+        memcpy(&mu[j], val, sizeof(DoubleNativeInt));
+    }
+    return mu;
+}
+static void with_precon(const std::vector<NativeInteger>& v, const std::vector<NativeInteger>& m, std::vector<NativeInteger>& pre) {
+    pre.resize(v.size());
+    for (size_t i = 0; i < v.size(); i++) pre[i] = v[i].PrepModMulConst(m[i]);
+}
+
+ref_behz* ref_behz_create(ref_ctx* QBsk, uint32_t nq, uint64_t t) {
+    auto* z = new ref_behz;
+    z->QBsk = QBsk; z->nq = nq; z->nb = QBsk->T - nq; z->t = NativeInteger(t);
+    const uint32_t nb = z->nb, nB = nb - 1;
+    auto all = moduli_of(QBsk);
+    z->moduliQ.assign(all.begin(), all.begin() + nq);
+    z->moduliBsk.assign(all.begin() + nq, all.end());
+    std::vector<NativeInteger> rootsQ;
+    for (uint32_t i = 0; i < nq; i++) rootsQ.push_back(QBsk->params->GetParams()[i]->GetRootOfUnity());
+    z->paramsQ = std::make_shared<ILDCRTParams<BigInteger>>(2 * QBsk->N, z->moduliQ, rootsQ);
+    const auto& mq = z->moduliQ;
+    const auto& mb = z->moduliBsk;
+    const NativeInteger msk = mb[nB];
+    const uint64_t mtilde = (uint64_t)1 << 16, gamma = (uint64_t)1 << 26;
+    BigInteger Q(1), B(1);
+    for (auto& qi : mq) Q *= BigInteger(qi);
+    for (uint32_t i = 0; i < nB; i++) B *= BigInteger(mb[i]);
+    z->modqMu   = barrett_mu_128(mq);
+    z->modbskMu = barrett_mu_128(mb);
+    const BigInteger bt(t), bmtilde(mtilde), bgamma(gamma);
+    z->tgamma = NativeInteger(t * gamma);
+    const BigInteger btgamma(z->tgamma);
+    z->mtildeQHatInvModq.resize(nq); z->tQHatInvModq.resize(nq); z->QHatModbsk.resize(nq); z->QHatModmtilde.resize(nq);
+    z->qInvModbsk.resize(nq); z->negInvqModtgamma.resize(nq); z->tgammaQHatInvModq.resize(nq); z->BModq.resize(nq);
+    for (uint32_t i = 0; i < nq; i++) {
+        const BigInteger qi(mq[i]);
+        const BigInteger QHat = Q / qi;
+        const BigInteger QHatInv = QHat.Mod(qi).ModInverse(qi);
+        z->mtildeQHatInvModq[i] = (QHatInv * bmtilde).Mod(qi).ConvertToInt();
+        z->tQHatInvModq[i]      = QHatInv.ModMul(bt, qi).ConvertToInt();
+        z->tgammaQHatInvModq[i] = (((QHatInv * bgamma) % qi) * bt % qi).ConvertToInt();
+        z->QHatModmtilde[i]     = QHat.Mod(bmtilde).ConvertToInt();
+        z->negInvqModtgamma[i]  = (BigInteger(z->tgamma - NativeInteger(1)) * qi.ModInverse(btgamma)).Mod(btgamma).ConvertToInt();
+        z->BModq[i]             = B.Mod(qi).ConvertToInt();
+        z->QHatModbsk[i].resize(nb); z->qInvModbsk[i].resize(nb);
+        for (uint32_t j = 0; j < nb; j++) {
+            z->QHatModbsk[i][j] = QHat.Mod(BigInteger(mb[j])).ConvertToInt();
+            z->qInvModbsk[i][j] = mq[i].ModInverse(mb[j]);
+        }
+    }
+    z->negQInvModmtilde = (BigInteger(mtilde - 1) * Q.ModInverse(bmtilde)).Mod(bmtilde).ConvertToInt();
+    z->QModbsk.resize(nb); z->mtildeInvModbsk.resize(nb); z->tQInvModbsk.resize(nb);
+    for (uint32_t j = 0; j < nb; j++) {
+        const BigInteger bj(mb[j]);
+        z->QModbsk[j]         = Q.Mod(bj).ConvertToInt();
+        z->mtildeInvModbsk[j] = (bmtilde % bj).ModInverse(bj).ConvertToInt();
+        z->tQInvModbsk[j]     = Q.ModInverse(bj).ModMul(bt, bj).ConvertToInt();
+    }
+    z->BHatInvModb.resize(nB); z->BHatModq.resize(nB); z->BHatModmsk.resize(nB);
+    for (uint32_t i = 0; i < nB; i++) {
+        const BigInteger bi(mb[i]);
+        const BigInteger BHat = B / bi;
+        z->BHatInvModb[i] = BHat.Mod(bi).ModInverse(bi).ConvertToInt();
+        z->BHatModmsk[i]  = BHat.Mod(BigInteger(msk)).ConvertToInt();
+        z->BHatModq[i].resize(nq);
+        for (uint32_t j = 0; j < nq; j++) z->BHatModq[i][j] = BHat.Mod(BigInteger(mq[j])).ConvertToInt();
+    }
+    z->BInvModmsk       = B.ModInverse(BigInteger(msk)).ConvertToInt();
+    z->BInvModmskPrecon = z->BInvModmsk.PrepModMulConst(msk);
+    with_precon(z->mtildeQHatInvModq, mq, z->mtildeQHatInvModqPrecon);
+    with_precon(z->tQHatInvModq, mq, z->tQHatInvModqPrecon);
+    with_precon(z->tgammaQHatInvModq, mq, z->tgammaQHatInvModqPrecon);
+    with_precon(z->BModq, mq, z->BModqPrecon);
+    with_precon(z->QModbsk, mb, z->QModbskPrecon);
+    with_precon(z->mtildeInvModbsk, mb, z->mtildeInvModbskPrecon);
+    with_precon(z->tQInvModbsk, mb, z->tQInvModbskPrecon);
+    with_precon(z->BHatInvModb, mb, z->BHatInvModbPrecon);
+    z->negInvqModtgammaPrecon.resize(nq);
+    for (uint32_t i = 0; i < nq; i++) z->negInvqModtgammaPrecon[i] = z->negInvqModtgamma[i].PrepModMulConst(z->tgamma);
+    return z;
+}
+void ref_behz_destroy(ref_behz* z) { delete z; }
+// table `which` in the numbering of oracle/fhe_oracle.h (orc_behz_table); returns the length in words
+size_t ref_behz_table(const ref_behz* z, int which, uint64_t* out) {
+    std::vector<uint64_t> v;
+    auto flat = [&](const std::vector<NativeInteger>& a) { for (auto& x : a) v.push_back(x.ConvertToInt()); };
+    auto flat2 = [&](const std::vector<std::vector<NativeInteger>>& a) { for (auto& r : a) flat(r); };
+    switch (which) {
+        case 0: flat(z->mtildeQHatInvModq); break;
+        case 1: flat2(z->QHatModbsk); break;
+        case 2: v = z->QHatModmtilde; break;
+        case 3: flat(z->QModbsk); break;
+        case 4: v.push_back(z->negQInvModmtilde); break;
+        case 5: flat(z->mtildeInvModbsk); break;
+        case 6: flat(z->tQHatInvModq); break;
+        case 7: flat2(z->qInvModbsk); break;
+        case 8: flat(z->tQInvModbsk); break;
+        case 9: flat(z->BHatInvModb); break;
+        case 10: flat2(z->BHatModq); break;
+        case 11: flat(z->BHatModmsk); break;
+        case 12: v.push_back(z->BInvModmsk.ConvertToInt()); break;
+        case 13: flat(z->BModq); break;
+        case 14: v.push_back(z->tgamma.ConvertToInt()); break;
+        case 15: flat(z->negInvqModtgamma); break;
+        case 16: flat(z->tgammaQHatInvModq); break;
+        default: return 0;
+    }
+    if (out) memcpy(out, v.data(), v.size() * 8);
+    return v.size();
+}
+
+static int behz_run(const std::function<void()>& f) {
+    int rc = 0;
+    std::string err;
+    serial_omp([&] {
+        try { f(); }
+        catch (const std::exception& e) { err = e.what(); rc = 1; }
+    });
+    if (rc) g_ref_err = err;
+    return rc;
+}
+// DCRTPoly::FastBaseConvqToBskMontgomery (dcrtpoly-impl.h:2069-2209), in place: the batch moves from Q to QBsk (EVALUATION)
+int ref_polys_behz_q_to_bsk(ref_polys* a, ref_behz* z) {
+    return behz_run([&] {
+        for (auto& poly : a->v)
+            poly.FastBaseConvqToBskMontgomery(z->QBsk->params, z->moduliQ, z->moduliBsk, z->modbskMu, z->mtildeQHatInvModq,
+                                              z->mtildeQHatInvModqPrecon, z->QHatModbsk, z->QHatModmtilde, z->QModbsk, z->QModbskPrecon,
+                                              z->negQInvModmtilde, z->mtildeInvModbsk, z->mtildeInvModbskPrecon);
+        a->ctx = z->QBsk;
+    });
+}
+// DCRTPoly::FastRNSFloorq (dcrtpoly-impl.h:2212-2271), in place over QBsk
+int ref_polys_behz_floor(ref_polys* a, ref_behz* z) {
+    return behz_run([&] {
+        for (auto& poly : a->v)
+            poly.FastRNSFloorq(z->t, z->moduliQ, z->moduliBsk, z->modbskMu, z->tQHatInvModq, z->tQHatInvModqPrecon, z->QHatModbsk,
+                               z->qInvModbsk, z->tQInvModbsk, z->tQInvModbskPrecon);
+    });
+}
+// DCRTPoly::FastBaseConvSK (dcrtpoly-impl.h:2309-2420), in place: the batch moves from QBsk to Q (`Q` = a context over the
+// first nq towers, used by ref_polys_store afterwards)
+int ref_polys_behz_conv_sk(ref_polys* a, ref_behz* z, ref_ctx* Q) {
+    return behz_run([&] {
+        for (auto& poly : a->v)
+            poly.FastBaseConvSK(z->paramsQ, z->modqMu, z->moduliBsk, z->modbskMu, z->BHatInvModb, z->BHatInvModbPrecon, z->BHatModmsk,
+                                z->BInvModmsk, z->BInvModmskPrecon, z->BHatModq, z->BModq, z->BModqPrecon);
+        a->ctx = Q;
+    });
+}
+// DCRTPoly::ScaleAndRound(moduliQ, t, tgamma, ...) -> NativePoly (dcrtpoly-impl.h:2005-2050): out [B][N]
+int ref_polys_behz_scale_and_round(const ref_polys* a, ref_behz* z, uint64_t* out) {
+    return behz_run([&] {
+        const uint32_t N = a->ctx->N;
+        size_t b = 0;
+        for (auto& poly : a->v) {
+            NativePoly r = poly.ScaleAndRound(z->moduliQ, z->t, z->tgamma, z->tgammaQHatInvModq, z->tgammaQHatInvModqPrecon,
+                                              z->negInvqModtgamma, z->negInvqModtgammaPrecon);
+            const auto& vals = r.GetValues();
+            for (uint32_t j = 0; j < N; j++) out[b * N + j] = vals[j].ConvertToInt();
+            b++;
+        }
+    });
+}
 
 }  // extern "C"

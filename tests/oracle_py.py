@@ -63,6 +63,12 @@ class Oracle:
             ("orc_decrypt_branch", ci, [vp, u32, u64]),
             ("orc_decrypt_tables", None, [vp, u32, u64, vp, vp, vp, vp]),
             ("orc_scale_and_round_native", None, [vp, vp, sz, u32, vp, u32, u64, vp, vp, vp, vp]),
+            ("orc_behz_create", vp, [vp, u32, u64]), ("orc_behz_destroy", None, [vp]),
+            ("orc_behz_table", sz, [vp, ci, vp]),
+            ("orc_behz_q_to_bsk_montgomery", None, [vp, vp, vp, sz, ci]),
+            ("orc_behz_fast_rns_floor_q", None, [vp, vp, sz]),
+            ("orc_behz_fast_base_conv_sk", None, [vp, vp, vp, sz]),
+            ("orc_behz_scale_and_round", None, [vp, vp, vp, sz]),
             ("orc_keyswitch_digits", u32, [u32, u32]),
             ("orc_keyswitch_precompute", None, [vp, u32, u32, vp, vp, sz]),
             ("orc_keyswitch_inner", None, [vp, u32, vp, vp, vp, vp, vp, sz]),
@@ -220,6 +226,54 @@ def _automap(self, n, k):
 
 OracleCtx.automorphism = _automorphism
 Oracle.automap = _automap
+
+
+class OracleBehz:
+    """BEHZ over QBsk = nq towers of Q followed by Bsk = B u {msk} (dcrtpoly-impl.h:2005-2050, 2069-2420)."""
+    NTABLES = 17
+
+    def __init__(self, o, n, q, psi, nq, t):
+        self.o, self.n, self.nq, self.nb, self.t = o, n, nq, len(q) - nq, int(t)
+        self.ctx = o.ctx(n, q, psi)
+        self.h = o.L.orc_behz_create(self.ctx.h, nq, int(t))
+        assert self.h, "orc_behz_create refused the shape"
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.o.L.orc_behz_destroy(self.h)
+            self.h = None
+
+    def table(self, which):
+        out = np.empty(self.o.L.orc_behz_table(self.h, which, None), np.uint64)
+        self.o.L.orc_behz_table(self.h, which, _p(out))
+        return out
+
+    def q_to_bsk_montgomery(self, x, fmt):
+        x = np.ascontiguousarray(x, np.uint64)
+        B = x.size // (self.nq * self.n)
+        out = np.empty((B, self.nq + self.nb, self.n), np.uint64)
+        self.o.L.orc_behz_q_to_bsk_montgomery(self.h, _p(out), _p(x), B, fmt)
+        return out
+
+    def fast_rns_floor_q(self, x):
+        x = np.array(x, dtype=np.uint64, copy=True)
+        B = x.size // ((self.nq + self.nb) * self.n)
+        self.o.L.orc_behz_fast_rns_floor_q(self.h, _p(x), B)
+        return x.reshape(B, self.nq + self.nb, self.n)
+
+    def fast_base_conv_sk(self, x):
+        x = np.ascontiguousarray(x, np.uint64)
+        B = x.size // ((self.nq + self.nb) * self.n)
+        out = np.empty((B, self.nq, self.n), np.uint64)
+        self.o.L.orc_behz_fast_base_conv_sk(self.h, _p(out), _p(x), B)
+        return out
+
+    def scale_and_round(self, x):
+        x = np.ascontiguousarray(x, np.uint64)
+        B = x.size // (self.nq * self.n)
+        out = np.empty((B, self.n), np.uint64)
+        self.o.L.orc_behz_scale_and_round(self.h, _p(out), _p(x), B)
+        return out
 
 
 class OracleBasis:
@@ -419,3 +473,4 @@ def load():
     if not os.path.exists(ORACLE_SO):
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "oracle"])
     return Oracle(ctypes.CDLL(ORACLE_SO))
+Oracle.behz = lambda self, n, q, psi, nq, t: OracleBehz(self, n, q, psi, nq, t)

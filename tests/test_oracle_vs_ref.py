@@ -449,3 +449,75 @@ def test_decrypt_scale_and_round_matches_reference(oracle, ref, nbits, towers, t
     assert np.array_equal(oracle.scale_and_round_native(x, n, q, t), out)
     assert (out < t).all()
     ref.ref_polys_free(hx); ref.ref_ctx_destroy(c)
+
+
+def behz_ring(oracle, nbits, n, nq, nB, msk_bits=0):
+    """Q, B and msk the way bfvrns-cryptoparameters.cpp:665-711 chains them (PreviousPrime below the last modulus of
+    Q); msk_bits > 0 replaces msk by a prime of that size (the scheme's `msk is large enough` loop, :700-706)."""
+    q, psi = oracle.gen_params(nbits, n, nq + nB + 1)
+    if msk_bits:
+        q[-1] = oracle.L.orc_next_prime(oracle.L.orc_first_prime(msk_bits, 2 * n), 2 * n)
+        psi[-1] = oracle.L.orc_root_of_unity(2 * n, int(q[-1]))
+    return q, psi
+
+
+# (bits, nq, |B|, t, msk bits): the scheme's shape |B| = nq, small and large t, msk above every q_i, a single tower
+BEHZ_CASES = [(60, 3, 3, 65537, 0), (45, 2, 2, 2, 0), (30, 4, 4, 1 << 20, 0), (40, 2, 2, 65537, 50), (55, 1, 1, 786433, 0),
+              (60, 5, 2, 65537, 0)]
+
+
+@pytest.mark.parametrize("nbits,nq,nB,t,msk_bits", BEHZ_CASES)
+def test_behz_matches_reference(oracle, ref, nbits, nq, nB, t, msk_bits):
+    """BEHZ restatement (tables and the four methods) against the reference's own DCRTPoly: FastBaseConvqToBskMontgomery
+    from either format, FastRNSFloorq (whole poly, incl. the twisted towers of Q it leaves behind), FastBaseConvSK and the
+    decryption ScaleAndRound(moduliQ, t, tgamma, ...), dcrtpoly-impl.h:2005-2050, 2069-2420."""
+    ref.ref_behz_create.restype = vp
+    ref.ref_behz_create.argtypes = [vp, u32, u64]
+    ref.ref_behz_destroy.argtypes = [vp]
+    ref.ref_behz_table.restype = sz
+    ref.ref_behz_table.argtypes = [vp, ci, vp]
+    ref.ref_polys_behz_q_to_bsk.argtypes = [vp, vp]
+    ref.ref_polys_behz_floor.argtypes = [vp, vp]
+    ref.ref_polys_behz_conv_sk.argtypes = [vp, vp, vp]
+    ref.ref_polys_behz_scale_and_round.argtypes = [vp, vp, vp]
+    n, B, nb = 128, 3, nB + 1
+    q, psi = behz_ring(oracle, nbits, n, nq, nB, msk_bits)
+    ob = oracle.behz(n, q, psi, nq, t)
+    cQBsk = ref.ref_ctx_create(n, nq + nb, p(q), p(psi))
+    cQ = ref.ref_ctx_create(n, nq, p(q[:nq].copy()), p(psi[:nq].copy()))
+    z = ref.ref_behz_create(cQBsk, nq, t)
+    for k in range(ob.NTABLES):
+        mine = ob.table(k)
+        theirs = np.empty(ref.ref_behz_table(z, k, None), np.uint64)
+        ref.ref_behz_table(z, k, p(theirs))
+        assert np.array_equal(mine, theirs), f"table {k}"
+    x = oracle.fill_ring(B, n, q[:nq].copy(), 311)
+    x[0, :, 0] = q[:nq] - np.uint64(1)
+    x[0, :, 1] = 0
+    for fmt in (0, 1):
+        h = ref.ref_polys_load(cQ, p(x), B, fmt)
+        assert ref.ref_polys_behz_q_to_bsk(h, z) == 0, ref.ref_last_error()
+        got = np.empty((B, nq + nb, n), np.uint64)
+        ref.ref_polys_store(h, p(got))
+        assert np.array_equal(ob.q_to_bsk_montgomery(x, fmt), got), f"FastBaseConvqToBskMontgomery format {fmt}"
+        ref.ref_polys_free(h)
+    y = oracle.fill_ring(B, n, q, 312)
+    y[0, :, 0] = q - np.uint64(1)
+    y[1, :, 3] = 0
+    h = ref.ref_polys_load(cQBsk, p(y), B, 1)
+    assert ref.ref_polys_behz_floor(h, z) == 0, ref.ref_last_error()
+    got = np.empty((B, nq + nb, n), np.uint64)
+    ref.ref_polys_store(h, p(got))
+    mine = ob.fast_rns_floor_q(y)
+    assert np.array_equal(mine, got), "FastRNSFloorq"
+    assert ref.ref_polys_behz_conv_sk(h, z, cQ) == 0, ref.ref_last_error()
+    got2 = np.empty((B, nq, n), np.uint64)
+    ref.ref_polys_store(h, p(got2))
+    assert np.array_equal(ob.fast_base_conv_sk(mine), got2), "FastBaseConvSK"
+    ref.ref_polys_free(h)
+    h = ref.ref_polys_load(cQ, p(x), B, 1)
+    out = np.empty((B, n), np.uint64)
+    assert ref.ref_polys_behz_scale_and_round(h, z, p(out)) == 0, ref.ref_last_error()
+    assert np.array_equal(ob.scale_and_round(x), out), "ScaleAndRound(moduliQ, t, tgamma, ...)"
+    ref.ref_polys_free(h)
+    ref.ref_behz_destroy(z); ref.ref_ctx_destroy(cQBsk); ref.ref_ctx_destroy(cQ)
