@@ -6,7 +6,7 @@ PKG     := upmem--openfhe_b200
 CSRC    := $(PKG)/csrc
 LIBDIR  := $(PKG)/lib
 NVFLAGS := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 --expt-relaxed-constexpr -Xcompiler -fPIC -Iinclude -I$(CSRC)
-CU      := $(CSRC)/elementwise.cu $(CSRC)/ntt.cu $(CSRC)/ntt_ws.cu $(CSRC)/modops.cu $(CSRC)/automorph.cu $(CSRC)/basis.cu $(CSRC)/keyswitch.cu $(CSRC)/decrypt.cu $(CSRC)/runtime.cu
+CU      := $(CSRC)/elementwise.cu $(CSRC)/ntt.cu $(CSRC)/ntt_ws.cu $(CSRC)/modops.cu $(CSRC)/automorph.cu $(CSRC)/basis.cu $(CSRC)/keyswitch.cu $(CSRC)/decrypt.cu $(CSRC)/behz.cu $(CSRC)/runtime.cu
 OBJ     := $(patsubst $(CSRC)/%.cu,$(LIBDIR)/obj/%.o,$(CU))
 HDR     := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h include/pim/*.h)
 

@@ -34,6 +34,9 @@
  *     ScaleAndRound   dcrtpoly-impl.h:1178-1358, 1876-1960        fhe_scale_and_round
  *   DCRTPolyImpl::DropLastElementAndScale / ModReduce            fhe_drop_last_element_and_scale / fhe_mod_reduce
  *     dcrtpoly-impl.h:746-812
+ *   DCRTPolyImpl::FastBaseConvqToBskMontgomery / FastRNSFloorq / fhe_fast_base_conv_q_to_bsk_montgomery / fhe_fast_rns_floor_q /
+ *     FastBaseConvSK / ScaleAndRound(moduliQ, t, tgamma, ...)     fhe_fast_base_conv_sk / fhe_scale_and_round_behz
+ *     dcrtpoly-impl.h:2005-2050, 2069-2420 (BFV, BEHZ)
  *   Serial::Serialize / Deserialize (SerType::BINARY) of a       fhe_serialize / fhe_deserialize
  *     DCRTPoly   utils/serial.h:99-115, dcrtpoly.h:349-365,
  *     poly.h:322-338, mubintvecnat.h:666-699
@@ -336,6 +339,35 @@ int fhe_deserialize(fhe_ring* ring, fhe_dptr dst, const void* src_host, size_t l
 
 /* seeded uniform coefficients in [0, q_tower) (synthetic inputs for tests and benchmarks) */
 int fhe_fill_uniform(fhe_ring* ring, fhe_dptr dst, size_t batch, uint64_t seed, int stream);
+
+/* ---- BFV, the BEHZ multiplication technique ------------------------------------------------------- */
+/* ring_qbsk: size_q towers of Q followed by Bsk = B u {msk} (at least one tower of B; msk last), with roots of unity,
+ * the ring CryptoParametersBFVRNS builds as m_paramsQBsk (src/pke/lib/scheme/bfvrns/bfvrns-cryptoparameters.cpp:
+ * 665-711).  Every table of :724-891 is derived here from the moduli and the plaintext modulus t (mtilde = 2^16,
+ * gamma = 2^26 are the scheme's constants): fhe_behz_table returns host copies, numbered 0 mtildeQHatInvModq[nq],
+ * 1 QHatModbsk[nq][nb], 2 QHatModmtilde[nq], 3 QModbsk[nb], 4 negQInvModmtilde, 5 mtildeInvModbsk[nb], 6 tQHatInvModq[nq],
+ * 7 qInvModbsk[nq][nb], 8 tQInvModbsk[nb], 9 BHatInvModb[nb-1], 10 BHatModq[nb-1][nq], 11 BHatModmsk[nb-1],
+ * 12 BInvModmsk, 13 BModq[nq], 14 tgamma, 15 negInvqModtgamma[nq], 16 tgammaQHatInvModq[nq].  The plan keeps scratch
+ * buffers: one per stream.  The ring must outlive it. */
+typedef struct fhe_behz fhe_behz;
+int fhe_behz_create(fhe_ring* ring_qbsk, uint32_t size_q, uint64_t t, fhe_behz** out);
+int fhe_behz_destroy(fhe_behz* plan);
+int fhe_behz_table(const fhe_behz* plan, int which, uint64_t* out, size_t* len);     /* out may be NULL (length only) */
+/* DCRTPolyImpl::FastBaseConvqToBskMontgomery (dcrtpoly-impl.h:2069-2209): src over Q [batch][nq][N] in `format`
+ * (0 EVALUATION, 1 COEFFICIENT) -> dst over QBsk [batch][nq+nb][N], EVALUATION.  src is not modified. */
+int fhe_fast_base_conv_q_to_bsk_montgomery(fhe_behz* plan, fhe_dptr dst_qbsk, fhe_dptr src_q, size_t batch, int format,
+                                           int stream);
+/* DCRTPolyImpl::FastRNSFloorq (dcrtpoly-impl.h:2212-2271), in place on x over QBsk [batch][nq+nb][N] (the scheme calls
+ * it in COEFFICIENT): the towers of Bsk receive floor(t/Q * x).  update_q != 0 also leaves the towers of Q multiplied
+ * by [t*(Q/q_i)^-1]_{q_i} as the reference does (:2233-2243; FastBaseConvSK overwrites them, so the scheme's sequence
+ * can pass 0 and save the pass). */
+int fhe_fast_rns_floor_q(fhe_behz* plan, fhe_dptr x_qbsk, size_t batch, int update_q, int stream);
+/* DCRTPolyImpl::FastBaseConvSK (dcrtpoly-impl.h:2309-2420): src over QBsk (only the towers of Bsk are read, none is
+ * modified) -> dst over Q [batch][nq][N]. */
+int fhe_fast_base_conv_sk(fhe_behz* plan, fhe_dptr dst_q, fhe_dptr src_qbsk, size_t batch, int stream);
+/* DCRTPolyImpl::ScaleAndRound(moduliQ, t, tgamma, tgammaQHatModq, .., negInvqModtgamma, ..) -> NativePoly
+ * (dcrtpoly-impl.h:2005-2050, BEHZ decryption): src over Q [batch][nq][N], COEFFICIENT -> dst [batch][N]. */
+int fhe_scale_and_round_behz(fhe_behz* plan, fhe_dptr dst, fhe_dptr src_q, size_t batch, int stream);
 
 /* ---- flat vectors with an explicit modulus (the PimData surface) ----------------------------- */
 int fhe_vec_op(fhe_ctx* ctx, int op, fhe_dptr dst, fhe_dptr a, fhe_dptr b, size_t n, uint64_t q, int stream);

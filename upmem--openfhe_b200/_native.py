@@ -98,6 +98,13 @@ SIGNATURES = {
     "fhe_decrypt_scale_destroy": (ci, [vp]),
     "fhe_decrypt_scale_tables": (ci, [vp, vp, vp, vp, vp, ctypes.POINTER(ci)]),
     "fhe_scale_and_round_native": (ci, [vp, u64, u64, sz, ci]),
+    "fhe_behz_create": (ci, [vp, u32, u64, ctypes.POINTER(vp)]),
+    "fhe_behz_destroy": (ci, [vp]),
+    "fhe_behz_table": (ci, [vp, ci, vp, ctypes.POINTER(sz)]),
+    "fhe_fast_base_conv_q_to_bsk_montgomery": (ci, [vp, u64, u64, sz, ci, ci]),
+    "fhe_fast_rns_floor_q": (ci, [vp, u64, sz, ci, ci]),
+    "fhe_fast_base_conv_sk": (ci, [vp, u64, u64, sz, ci]),
+    "fhe_scale_and_round_behz": (ci, [vp, u64, u64, sz, ci]),
     "fhe_keyswitch_create": (ci, [vp, u32, u32, ctypes.POINTER(vp)]),
     "fhe_keyswitch_destroy": (ci, [vp]),
     "fhe_keyswitch_digits": (u32, [vp]),

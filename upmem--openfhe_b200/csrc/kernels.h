@@ -122,6 +122,33 @@ struct DecryptDev {
 // dst [batch][N] = ScaleAndRound of src [batch][T][N] (COEFFICIENT)
 cudaError_t launch_decrypt_scale(const DecryptDev& dd, uint64_t* dst, const uint64_t* src, size_t batch, uint32_t logN,
                                  cudaStream_t st);
+// BEHZ (dcrtpoly-impl.h:2005-2050, 2069-2420): per-tower constants of the corrections that follow the fast base
+// conversions (behz.cu).  nq towers of Q, nb towers of Bsk = B u {msk} (msk last).
+struct BehzDev {
+    uint32_t nq, nb;
+    const ulonglong4* qk;        // [nq] {q_i, [mtilde*(Q/q_i)^-1]_{q_i}, its Shoup companion, [Q/q_i]_{mtilde}}
+    const ulonglong4* bk;        // [nb] {[Q]_{bsk_j}, companion, [mtilde^-1]_{bsk_j}, companion}
+    const uint64_t* bsk;         // [nb] bsk_j
+    const ulonglong4* fk;        // [nq+nb] {c, companion, modulus, 0}: c = [t*(Q/q_i)^-1]_{q_i} over Q, [t*Q^-1]_{bsk_j} over Bsk
+    const ulonglong4* sk;        // [nq] {[B]_{q_i}, companion, q_i, 0}
+    const ulonglong4* dk;        // [nq] {[t*gamma*(Q/q_i)^-1]_{q_i}, companion, [-q_i^-1]_{t*gamma}, companion}
+    uint64_t neg_qinv_mtilde;    // [-Q^-1]_{mtilde}
+    uint64_t msk, binv_msk, binv_mskp;      // msk, [B^-1]_{msk} and its companion
+    uint64_t tgamma;             // t * 2^26
+};
+// x [batch][nq+nb][N]: towers nq.. = FastBaseConv(|x*mtilde|_q, q, Bsk) on entry, Montgomery-reduced on exit; coef
+// [batch][nq][N] = the input in COEFFICIENT format (must not overlap x)
+cudaError_t launch_behz_montgomery(const BehzDev& d, uint64_t* x, const uint64_t* coef, size_t batch, uint32_t logN, cudaStream_t st);
+// in place on x [batch][nq+nb][N] with conv [batch][nb][N] = FastBaseConv(|t*x|_q, q, Bsk); update_q: also leave the towers of Q
+// multiplied by [t*(Q/q_i)^-1]_{q_i} as the reference does
+cudaError_t launch_behz_floor(const BehzDev& d, uint64_t* x, const uint64_t* conv, size_t batch, uint32_t logN, bool update_q,
+                              cudaStream_t st);
+// dst [batch][nq][N] from conv [batch][nq+1][N] (FastBaseConv(x, B, q) and FastBaseConv(x, B, msk)) and the msk tower of the
+// input (xsk, xT towers per polynomial)
+cudaError_t launch_behz_sk(const BehzDev& d, uint64_t* dst, const uint64_t* conv, const uint64_t* xsk, uint32_t xT, size_t batch,
+                           uint32_t logN, cudaStream_t st);
+// dst [batch][N] = ScaleAndRound(moduliQ, t, tgamma, ...) of src [batch][nq][N] (COEFFICIENT)
+cudaError_t launch_behz_decrypt(const BehzDev& d, uint64_t* dst, const uint64_t* src, size_t batch, uint32_t logN, cudaStream_t st);
 // Counter-based uniform fill in [0, q_t) per tower (same definition as the test oracle's generator).
 cudaError_t launch_fill_uniform(const RingDev& r, uint64_t* dst, size_t batch, uint64_t seed,
                                 cudaStream_t st);

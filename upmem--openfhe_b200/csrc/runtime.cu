@@ -2087,6 +2087,236 @@ extern "C" int fhe_keyswitch_hybrid(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1
 }
 
 // ---------------------------------------------------------------------------------------------
+// BEHZ (dcrtpoly-impl.h:2005-2050, 2069-2420): the BFV multiplication technique that the HPS plans above do not cover.
+// A plan over the ring Q u Bsk holds the scheme's tables (bfvrns-cryptoparameters.cpp:662-885, derived from the
+// moduli and t), three conversions built as fhe_basis objects with those tables, and the correction constants of
+// behz.cu.
+// ---------------------------------------------------------------------------------------------
+enum { BEHZ_TABLES = 17 };
+struct fhe_behz {
+    fhe_ctx* ctx = nullptr;
+    fhe_ring* qbsk = nullptr;                     // caller's ring: nq towers of Q, then B, then msk
+    uint32_t nq = 0, nb = 0;
+    uint64_t t = 0;
+    fhe_ring *q = nullptr, *bsk = nullptr, *b = nullptr;        // views
+    fhe_ring* qm = nullptr;                       // Q followed by msk (targets of FastBaseConvSK's two conversions), no NTT
+    fhe_basis *mont = nullptr, *floor = nullptr, *sk = nullptr;
+    std::vector<uint64_t> tab[BEHZ_TABLES];
+    BehzDev dev{};
+    void *d_qk = nullptr, *d_bk = nullptr, *d_bsk = nullptr, *d_fk = nullptr, *d_sk = nullptr, *d_dk = nullptr;
+    Scratch coef, conv;
+};
+
+extern "C" int fhe_behz_destroy(fhe_behz* z) {
+    if (!z) return FHE_OK;
+    cudaSetDevice(z->ctx->device);
+    cudaDeviceSynchronize();
+    fhe_basis_destroy(z->mont); fhe_basis_destroy(z->floor); fhe_basis_destroy(z->sk);
+    fhe_ring_destroy(z->q); fhe_ring_destroy(z->bsk); fhe_ring_destroy(z->b); fhe_ring_destroy(z->qm);
+    for (void* p : {z->d_qk, z->d_bk, z->d_bsk, z->d_fk, z->d_sk, z->d_dk})
+        if (p) arena_park(z->ctx, p);
+    z->coef.drop(z->ctx); z->conv.drop(z->ctx);
+    delete z;
+    return FHE_OK;
+}
+
+static uint64_t prod_all_mod(const std::vector<uint64_t>& f, uint64_t m) { return prod_mod(f, (size_t)-1, m); }
+
+extern "C" int fhe_behz_create(fhe_ring* ring_qbsk, uint32_t size_q, uint64_t t, fhe_behz** out) {
+    if (!ring_qbsk || !out) return fail(FHE_EINVAL, "fhe_behz_create: null argument");
+    *out = nullptr;
+    const uint32_t T = ring_qbsk->dev.T;
+    if (size_q == 0 || size_q + 2 > T)
+        return fail(FHE_EINVAL, "fhe_behz_create: size_q=%u must leave at least one tower of B and msk in the ring's %u", size_q, T);
+    if (T > 256) return fail(FHE_EUNSUPPORTED, "fhe_behz_create: more than 256 towers");
+    if (ring_qbsk->dev.N < 2) return fail(FHE_EUNSUPPORTED, "fhe_behz_create: N must be at least 2");
+    if (t < 2 || t >= (1ull << 32)) return fail(FHE_EINVAL, "fhe_behz_create: plaintext modulus %llu not in [2, 2^32) (t * 2^26 has to stay below 2^58)", (unsigned long long)t);
+    const uint32_t nq = size_q, nb = T - nq, nB = nb - 1;
+    const std::vector<uint64_t> q(ring_qbsk->q.begin(), ring_qbsk->q.begin() + nq);
+    const std::vector<uint64_t> bsk(ring_qbsk->q.begin() + nq, ring_qbsk->q.end());
+    const std::vector<uint64_t> B(bsk.begin(), bsk.begin() + nB);
+    const uint64_t msk = bsk[nB], mtilde = 1ull << 16, gamma = 1ull << 26, tgamma = t * gamma;
+    for (uint64_t m : ring_qbsk->q)
+        if (!(m & 1)) return fail(FHE_EINVAL, "fhe_behz_create: modulus %llu is even", (unsigned long long)m);
+    for (uint64_t m : bsk)          // "mtilde = 2^16 < all moduli of Bsk", dcrtpoly-impl.h:2178
+        if (m <= mtilde) return fail(FHE_EINVAL, "fhe_behz_create: modulus %llu of Bsk is not above mtilde = 2^16", (unsigned long long)m);
+    auto* z = new fhe_behz;
+    z->ctx = ring_qbsk->ctx; z->qbsk = ring_qbsk; z->nq = nq; z->nb = nb; z->t = t;
+    auto bad = [&](const char* what) { fhe_behz_destroy(z); return fail(FHE_EINVAL, "fhe_behz_create: %s", what); };
+    // ---- tables, numbered as include/fhe_b200.h lists them (bfvrns-cryptoparameters.cpp:724-891) ----
+    std::vector<uint64_t> hatinv(nq);
+    for (uint32_t i = 0; i < nq; i++) {
+        hatinv[i] = host::invmod(prod_mod(q, i, q[i]), q[i]);
+        if (!hatinv[i]) return bad("the moduli of Q are not pairwise coprime");
+    }
+    auto& tb = z->tab;
+    tb[0].resize(nq); tb[1].resize((size_t)nq * nb); tb[2].resize(nq); tb[6].resize(nq); tb[7].resize((size_t)nq * nb);
+    tb[13].resize(nq); tb[15].resize(nq); tb[16].resize(nq);
+    for (uint32_t i = 0; i < nq; i++) {
+        tb[0][i] = host::mulmod(hatinv[i], mtilde % q[i], q[i]);
+        tb[6][i] = host::mulmod(hatinv[i], t % q[i], q[i]);
+        tb[2][i] = prod_mod(q, i, mtilde);
+        tb[13][i] = prod_all_mod(B, q[i]);
+        const uint64_t qinv_tg = host::invmod(q[i] % tgamma, tgamma);
+        if (!qinv_tg) return bad("a modulus of Q shares a factor with t");
+        tb[15][i] = host::mulmod(tgamma - 1, qinv_tg, tgamma);
+        tb[16][i] = host::mulmod(host::mulmod(hatinv[i], gamma % q[i], q[i]), t % q[i], q[i]);
+        for (uint32_t j = 0; j < nb; j++) {
+            tb[1][(size_t)i * nb + j] = prod_mod(q, i, bsk[j]);
+            const uint64_t inv = host::invmod(q[i] % bsk[j], bsk[j]);
+            if (!inv) return bad("a modulus of Q is not invertible modulo a modulus of Bsk");
+            tb[7][(size_t)i * nb + j] = inv;
+        }
+    }
+    tb[3].resize(nb); tb[5].resize(nb); tb[8].resize(nb);
+    for (uint32_t j = 0; j < nb; j++) {
+        tb[3][j] = prod_all_mod(q, bsk[j]);
+        tb[5][j] = host::invmod(mtilde % bsk[j], bsk[j]);
+        const uint64_t qinv = host::invmod(tb[3][j], bsk[j]);
+        if (!qinv || !tb[5][j]) return bad("Q or mtilde is not invertible modulo a modulus of Bsk");
+        tb[8][j] = host::mulmod(qinv, t % bsk[j], bsk[j]);
+    }
+    tb[4].assign(1, host::mulmod(mtilde - 1, host::invmod(prod_all_mod(q, mtilde), mtilde), mtilde));
+    tb[9].resize(nB); tb[10].resize((size_t)nB * nq); tb[11].resize(nB);
+    for (uint32_t i = 0; i < nB; i++) {
+        tb[9][i] = host::invmod(prod_mod(B, i, B[i]), B[i]);
+        if (!tb[9][i]) return bad("the moduli of B are not pairwise coprime");
+        tb[11][i] = prod_mod(B, i, msk);
+        for (uint32_t j = 0; j < nq; j++) tb[10][(size_t)i * nq + j] = prod_mod(B, i, q[j]);
+    }
+    tb[12].assign(1, host::invmod(prod_all_mod(B, msk), msk));
+    if (!tb[12][0]) return bad("B is not invertible modulo msk");
+    tb[14].assign(1, tgamma);
+    // ---- views, conversions, constants ----
+    std::vector<uint64_t> qm(q);
+    qm.push_back(msk);
+    std::vector<uint64_t> sk_hat((size_t)nB * (nq + 1));                  // [B/b_i]_{q_j} with [B/b_i]_{msk} as the last column
+    for (uint32_t i = 0; i < nB; i++) {
+        for (uint32_t j = 0; j < nq; j++) sk_hat[(size_t)i * (nq + 1) + j] = tb[10][(size_t)i * nq + j];
+        sk_hat[(size_t)i * (nq + 1) + nq] = tb[11][i];
+    }
+    int rc;
+    if ((rc = fhe_ring_view(ring_qbsk, 0, nq, &z->q)) || (rc = fhe_ring_view(ring_qbsk, nq, nb, &z->bsk)) ||
+        (rc = fhe_ring_view(ring_qbsk, nq, nB, &z->b)) ||
+        (rc = fhe_ring_create(z->ctx, ring_qbsk->dev.N, nq + 1, qm.data(), nullptr, &z->qm)) ||
+        (rc = fhe_basis_create(z->q, z->bsk, tb[0].data(), tb[1].data(), &z->mont)) ||
+        (rc = fhe_basis_create(z->q, z->bsk, tb[6].data(), tb[7].data(), &z->floor)) ||
+        (rc = fhe_basis_create(z->b, z->qm, tb[9].data(), sk_hat.data(), &z->sk))) {
+        fhe_behz_destroy(z);
+        return rc;
+    }
+    std::vector<ulonglong4> qk(nq), bk(nb), fk(nq + nb), sk(nq), dk(nq);
+    for (uint32_t i = 0; i < nq; i++) {
+        qk[i] = make_ulonglong4(q[i], tb[0][i], host::shoup_companion(tb[0][i], q[i]), tb[2][i]);
+        fk[i] = make_ulonglong4(tb[6][i], host::shoup_companion(tb[6][i], q[i]), q[i], 0);
+        sk[i] = make_ulonglong4(tb[13][i], host::shoup_companion(tb[13][i], q[i]), q[i], 0);
+        dk[i] = make_ulonglong4(tb[16][i], host::shoup_companion(tb[16][i], q[i]), tb[15][i], host::shoup_companion(tb[15][i], tgamma));
+    }
+    for (uint32_t j = 0; j < nb; j++) {
+        bk[j] = make_ulonglong4(tb[3][j], host::shoup_companion(tb[3][j], bsk[j]), tb[5][j], host::shoup_companion(tb[5][j], bsk[j]));
+        fk[nq + j] = make_ulonglong4(tb[8][j], host::shoup_companion(tb[8][j], bsk[j]), bsk[j], 0);
+    }
+    if ((rc = upload(z->ctx, qk, &z->d_qk)) || (rc = upload(z->ctx, bk, &z->d_bk)) || (rc = upload(z->ctx, bsk, &z->d_bsk)) ||
+        (rc = upload(z->ctx, fk, &z->d_fk)) || (rc = upload(z->ctx, sk, &z->d_sk)) || (rc = upload(z->ctx, dk, &z->d_dk))) {
+        fhe_behz_destroy(z);
+        return rc;
+    }
+    BehzDev& d = z->dev;
+    d.nq = nq; d.nb = nb;
+    d.qk = (const ulonglong4*)z->d_qk; d.bk = (const ulonglong4*)z->d_bk; d.bsk = (const uint64_t*)z->d_bsk;
+    d.fk = (const ulonglong4*)z->d_fk; d.sk = (const ulonglong4*)z->d_sk; d.dk = (const ulonglong4*)z->d_dk;
+    d.neg_qinv_mtilde = tb[4][0];
+    d.msk = msk; d.binv_msk = tb[12][0]; d.binv_mskp = host::shoup_companion(tb[12][0], msk);
+    d.tgamma = tgamma;
+    *out = z;
+    return FHE_OK;
+}
+
+extern "C" int fhe_behz_table(const fhe_behz* z, int which, uint64_t* out, size_t* len) {
+    if (!z) return fail(FHE_EINVAL, "null BEHZ plan");
+    if (which < 0 || which >= BEHZ_TABLES) return fail(FHE_EINVAL, "fhe_behz_table: table %d not in [0, %d)", which, (int)BEHZ_TABLES);
+    if (len) *len = z->tab[which].size();
+    if (out) memcpy(out, z->tab[which].data(), z->tab[which].size() * 8);
+    return FHE_OK;
+}
+
+static int behz_enter(fhe_behz* z, int stream, StreamRef* s, const char* who, size_t batch, std::initializer_list<fhe_dptr> ptrs) {
+    if (!z) return fail(FHE_EINVAL, "null BEHZ plan");
+    int rc = ring_stream(z->qbsk, stream, s);
+    if (rc) return rc;
+    if (batch == 0) return FHE_OK;
+    fhe_dptr all = 0;
+    for (fhe_dptr p : ptrs) {
+        if (!p) return fail(FHE_EINVAL, "%s: null device pointer", who);
+        all |= p;
+    }
+    if (all & 15) return fail(FHE_EINVAL, "%s: device pointers must be 16-byte aligned", who);
+    return FHE_OK;
+}
+
+extern "C" int fhe_fast_base_conv_q_to_bsk_montgomery(fhe_behz* z, fhe_dptr dst_qbsk, fhe_dptr src_q, size_t batch, int format,
+                                                      int stream) {
+    const char* who = "fhe_fast_base_conv_q_to_bsk_montgomery";
+    StreamRef s;
+    int rc = behz_enter(z, stream, &s, who, batch, {dst_qbsk, src_q});
+    if (rc || batch == 0) return rc;
+    if (format != 0 && format != 1) return fail(FHE_EINVAL, "%s: format must be 0 (EVALUATION) or 1 (COEFFICIENT)", who);
+    if (dst_qbsk == src_q) return fail(FHE_EINVAL, "%s: dst must not alias src (the towers are laid out differently)", who);
+    const uint32_t N = z->qbsk->dev.N, logN = z->qbsk->dev.logN, nq = z->nq, T = z->nq + z->nb;
+    uint64_t* dst = (uint64_t*)(uintptr_t)dst_qbsk;
+    const uint64_t* src = (const uint64_t*)(uintptr_t)src_q;
+    const uint64_t* coef = src;
+    if (format == 0) {                                   // :2087-2090 the input's COEFFICIENT form, in scratch
+        if ((rc = z->coef.need(z->ctx, batch * nq * (size_t)N * 8))) return rc;
+        if ((rc = ring_ntt(z->q, (uint64_t*)z->coef.p, batch, true, s, who, src, nq, nq))) return rc;
+        coef = (const uint64_t*)z->coef.p;
+    }
+    // step 0 modulo Bsk (:2103-2127), written where the towers of Bsk belong; then modulo mtilde and step 1 (:2148-2190)
+    CUDA_TRY(launch_basis_switch(z->mont->dev, dst, T, nq, coef, nq, 0, batch, logN, false, s));
+    CUDA_TRY(launch_behz_montgomery(z->dev, dst, coef, batch, logN, s));
+    if (format == 0) CUDA_TRY(copy_towers(dst, T, 0, src, nq, 0, nq, batch, N, s));          // :2194-2197
+    else if ((rc = ring_ntt(z->q, dst, batch, false, s, who, src, T, nq))) return rc;        // :2198-2202
+    return ring_ntt(z->bsk, dst + (size_t)nq * N, batch, false, s, who, nullptr, T);         // :2204-2206
+}
+
+extern "C" int fhe_fast_rns_floor_q(fhe_behz* z, fhe_dptr x_qbsk, size_t batch, int update_q, int stream) {
+    const char* who = "fhe_fast_rns_floor_q";
+    StreamRef s;
+    int rc = behz_enter(z, stream, &s, who, batch, {x_qbsk});
+    if (rc || batch == 0) return rc;
+    const uint32_t N = z->qbsk->dev.N, logN = z->qbsk->dev.logN, nq = z->nq, nb = z->nb, T = nq + nb;
+    uint64_t* x = (uint64_t*)(uintptr_t)x_qbsk;
+    if ((rc = z->conv.need(z->ctx, batch * (size_t)std::max(nb, nq + 1) * N * 8))) return rc;
+    // FastBaseConv(|t*x|_q, q, Bsk) (:2233-2256), then the subtraction (:2260-2269)
+    CUDA_TRY(launch_basis_switch(z->floor->dev, (uint64_t*)z->conv.p, nb, 0, x, T, 0, batch, logN, false, s));
+    CUDA_TRY(launch_behz_floor(z->dev, x, (const uint64_t*)z->conv.p, batch, logN, update_q != 0, s));
+    return FHE_OK;
+}
+
+extern "C" int fhe_fast_base_conv_sk(fhe_behz* z, fhe_dptr dst_q, fhe_dptr src_qbsk, size_t batch, int stream) {
+    const char* who = "fhe_fast_base_conv_sk";
+    StreamRef s;
+    int rc = behz_enter(z, stream, &s, who, batch, {dst_q, src_qbsk});
+    if (rc || batch == 0) return rc;
+    if (dst_q == src_qbsk) return fail(FHE_EINVAL, "%s: dst must not alias src (the towers are laid out differently)", who);
+    const uint32_t N = z->qbsk->dev.N, logN = z->qbsk->dev.logN, nq = z->nq, nb = z->nb, T = nq + nb;
+    const uint64_t* src = (const uint64_t*)(uintptr_t)src_qbsk;
+    if ((rc = z->conv.need(z->ctx, batch * (size_t)std::max(nb, nq + 1) * N * 8))) return rc;
+    // FastBaseconv(x, B, q) and FastBaseConv(x, B, msk) in one conversion B -> Q u {msk} (:2327-2364), then alpha_sk (:2366-2388)
+    CUDA_TRY(launch_basis_switch(z->sk->dev, (uint64_t*)z->conv.p, nq + 1, 0, src, T, nq, batch, logN, false, s));
+    CUDA_TRY(launch_behz_sk(z->dev, (uint64_t*)(uintptr_t)dst_q, (const uint64_t*)z->conv.p, src + (size_t)(T - 1) * N, T, batch, logN, s));
+    return FHE_OK;
+}
+
+extern "C" int fhe_scale_and_round_behz(fhe_behz* z, fhe_dptr dst, fhe_dptr src_q, size_t batch, int stream) {
+    StreamRef s;
+    int rc = behz_enter(z, stream, &s, "fhe_scale_and_round_behz", batch, {dst, src_q});
+    if (rc || batch == 0) return rc;
+    CUDA_TRY(launch_behz_decrypt(z->dev, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)src_q, batch, z->qbsk->dev.logN, s));
+    return FHE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // several devices of one node: the batch is split in contiguous blocks, one per device, every
 // device holds the ring's tables, no collective runs inside the path.  NCCL (loaded at run time: libnccl.so.2)
 // carries only the optional gather of results over NVLink / NVSwitch, on the library's own streams.

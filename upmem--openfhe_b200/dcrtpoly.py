@@ -761,6 +761,80 @@ class KeySwitch:
         N.check(N.lib.fhe_keyswitch_hybrid(self.h, ct0, ct1, c, evk_b, evk_a, batch, int(t), stream))
 
 
+class Behz:
+    """The BEHZ set of DCRTPolyImpl (dcrtpoly-impl.h:2005-2050, 2069-2420) over `ring_qbsk` = size_q towers of Q followed
+    by Bsk = B u {msk}; every table of bfvrns-cryptoparameters.cpp:724-891 is derived on the host from the moduli and t."""
+    NTABLES = 17
+
+    def __init__(self, ring_qbsk, size_q, t):
+        self.ring, self.nq, self.nb, self.t = ring_qbsk, size_q, ring_qbsk.towers - size_q, int(t)
+        h = ctypes.c_void_p()
+        N.check(N.lib.fhe_behz_create(ring_qbsk.h, size_q, self.t, ctypes.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_behz_destroy(self.h)
+            self.h = None
+
+    def table(self, which):
+        n = ctypes.c_size_t()
+        N.check(N.lib.fhe_behz_table(self.h, which, None, ctypes.byref(n)))
+        out = np.zeros(n.value, np.uint64)
+        N.check(N.lib.fhe_behz_table(self.h, which, _ptr(out), None))
+        return out
+
+    def q_to_bsk_montgomery(self, dst_qbsk, src_q, batch, fmt, stream=0):
+        N.check(N.lib.fhe_fast_base_conv_q_to_bsk_montgomery(self.h, dst_qbsk, src_q, batch, fmt, stream))
+
+    def fast_rns_floor_q(self, x_qbsk, batch, update_q=True, stream=0):
+        N.check(N.lib.fhe_fast_rns_floor_q(self.h, x_qbsk, batch, 1 if update_q else 0, stream))
+
+    def fast_base_conv_sk(self, dst_q, src_qbsk, batch, stream=0):
+        N.check(N.lib.fhe_fast_base_conv_sk(self.h, dst_q, src_qbsk, batch, stream))
+
+    def scale_and_round(self, dst, src_q, batch, stream=0):
+        N.check(N.lib.fhe_scale_and_round_behz(self.h, dst, src_q, batch, stream))
+
+
+class BfvBehzMult:
+    """The RNS core of BFVrns EvalMult with the BEHZ technique (src/pke/lib/scheme/bfvrns/bfvrns-leveledshe.cpp:275-297,
+    322-334, 367-388) composed from the device calls: FastBaseConvqToBskMontgomery of the four input polynomials Q -> QBsk,
+    the fused 2 x 2 tensor product over QBsk, inverse NTT, FastRNSFloorq, FastBaseConvSK back to Q.
+    Inputs: a = (a0, a1), b = (b0, b1) device addresses over Q in EVALUATION; outputs c = (c0, c1, c2) over Q in COEFFICIENT."""
+
+    def __init__(self, ring_qbsk, size_q, t):
+        self.ring = ring_qbsk
+        self.behz = Behz(ring_qbsk, size_q, t)
+        self.batch, self.bufs = 0, []
+
+    def _reserve(self, batch):
+        if batch <= self.batch:
+            return
+        be = self.ring.be
+        for p in self.bufs:
+            be.free(p)
+        self.bufs = [be.alloc(self.ring.words(batch) * 8) for _ in range(7)]
+        self.batch = batch
+
+    def __call__(self, c, a, b, batch, stream=0):
+        self._reserve(batch)
+        e, t = self.bufs[0:4], self.bufs[4:7]
+        for dst, src in zip(e, (a[0], a[1], b[0], b[1])):
+            self.behz.q_to_bsk_montgomery(dst, src, batch, EVALUATION, stream)
+        self.ring.ct_multiply(t, e[0:2], e[2:4], batch, 0, stream)
+        for k in range(3):
+            self.ring.ntt(t[k], batch, inverse=True, stream=stream)
+            self.behz.fast_rns_floor_q(t[k], batch, update_q=False, stream=stream)     # the towers of Q are dead from here on
+            self.behz.fast_base_conv_sk(c[k], t[k], batch, stream)
+
+    def close(self):
+        for p in self.bufs:
+            self.ring.be.free(p)
+        self.bufs, self.batch = [], 0
+        self.behz.close()
+
+
 class DecryptScale:
     """BFV decryption's scaling step, DCRTPolyImpl::ScaleAndRound(t, ...) -> NativePoly (dcrtpoly-impl.h:1537-1816):
     src over `ring` (COEFFICIENT) -> [batch][N] values modulo t.  tables = (modt, b_modt, frac, b_frac) as the scheme
