@@ -362,6 +362,16 @@ int fhe_fast_base_conv_q_to_bsk_montgomery(fhe_behz* plan, fhe_dptr dst_qbsk, fh
  * by [t*(Q/q_i)^-1]_{q_i} as the reference does (:2233-2243; FastBaseConvSK overwrites them, so the scheme's sequence
  * can pass 0 and save the pass). */
 int fhe_fast_rns_floor_q(fhe_behz* plan, fhe_dptr x_qbsk, size_t batch, int update_q, int stream);
+/* fhe_fast_rns_floor_q for callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same arguments and the
+ * same result; the conversion's intermediate lives in a static 8 MiB device array instead of the plan's scratch, so
+ * batch * (towers of Bsk) * N must not exceed 2^20 words (FHE_EINVAL otherwise), and the call performs no cudaMalloc /
+ * cudaFree / arena allocation.  Every GPU that loads the library holds the 8 MiB until exit.  All calls on a device share
+ * the array (nothing in it has to start at zero: the first kernel writes every word the second reads; it keeps the last
+ * call's contents): calls that overlap on the GPU - different streams, or different plans - race; serialise them.  The
+ * first call on a device resolves the array's device address (cudaGetSymbolAddress): under graph capture make one
+ * call outside the capture first. */
+int fhe_fast_rns_floor_q_noalloc(fhe_behz* plan, fhe_dptr x_qbsk, size_t batch, int update_q, int stream);
 /* DCRTPolyImpl::FastBaseConvSK (dcrtpoly-impl.h:2309-2420): src over QBsk (only the towers of Bsk are read, none is
  * modified) -> dst over Q [batch][nq][N]. */
 int fhe_fast_base_conv_sk(fhe_behz* plan, fhe_dptr dst_q, fhe_dptr src_qbsk, size_t batch, int stream);

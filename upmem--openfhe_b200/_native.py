@@ -103,6 +103,7 @@ SIGNATURES = {
     "fhe_behz_table": (ci, [vp, ci, vp, ctypes.POINTER(sz)]),
     "fhe_fast_base_conv_q_to_bsk_montgomery": (ci, [vp, u64, u64, sz, ci, ci]),
     "fhe_fast_rns_floor_q": (ci, [vp, u64, sz, ci, ci]),
+    "fhe_fast_rns_floor_q_noalloc": (ci, [vp, u64, sz, ci, ci]),
     "fhe_fast_base_conv_sk": (ci, [vp, u64, u64, sz, ci]),
     "fhe_scale_and_round_behz": (ci, [vp, u64, u64, sz, ci]),
     "fhe_keyswitch_create": (ci, [vp, u32, u32, ctypes.POINTER(vp)]),

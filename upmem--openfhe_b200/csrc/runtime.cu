@@ -2293,6 +2293,48 @@ extern "C" int fhe_fast_rns_floor_q(fhe_behz* z, fhe_dptr x_qbsk, size_t batch, 
     return FHE_OK;
 }
 
+// fhe_fast_rns_floor_q without any allocation (no counterpart in the reference; added
+// for callers that may not allocate: CUDA graph capture, serving loops).  The conversion's intermediate
+// [batch][nb][N] lives in a file-scope device array instead of the plan's arena scratch.  The array's name is only a
+// host-side stand-in in host code: its device address is resolved with cudaGetSymbolAddress, once per device, with
+// that device current, and that address is what the kernels receive.
+#define FHE_NOALLOC_SCRATCH_WORDS (1u << 20)                       /* 8 MiB per GPU that loads the library */
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[FHE_NOALLOC_SCRATCH_WORDS];
+
+static int noalloc_scratch(int device, uint64_t** out) {
+    static std::mutex mu;
+    static uint64_t* addr[64] = {};
+    if (device < 0 || device >= 64) return fail(FHE_EUNSUPPORTED, "no-alloc scratch: device %d not in [0, 64)", device);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!addr[device]) {
+        void* p = nullptr;
+        CUDA_TRY(cudaSetDevice(device));
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) return fail(FHE_ECUDA, "no-alloc scratch: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        addr[device] = (uint64_t*)p;
+    }
+    *out = addr[device];
+    return FHE_OK;
+}
+
+extern "C" int fhe_fast_rns_floor_q_noalloc(fhe_behz* z, fhe_dptr x_qbsk, size_t batch, int update_q, int stream) {
+    const char* who = "fhe_fast_rns_floor_q_noalloc";
+    StreamRef s;
+    int rc = behz_enter(z, stream, &s, who, batch, {x_qbsk});
+    if (rc || batch == 0) return rc;
+    const uint32_t N = z->qbsk->dev.N, logN = z->qbsk->dev.logN, nq = z->nq, nb = z->nb, T = nq + nb;
+    if (batch > FHE_NOALLOC_SCRATCH_WORDS / ((size_t)nb * N))
+        return fail(FHE_EINVAL, "%s: batch * towers of Bsk * N = %zu * %u * %u words exceeds the static scratch of %u words (8 MiB); "
+                    "use fhe_fast_rns_floor_q", who, batch, nb, N, (unsigned)FHE_NOALLOC_SCRATCH_WORDS);
+    uint64_t* conv = nullptr;
+    if ((rc = noalloc_scratch(z->ctx->device, &conv))) return rc;
+    uint64_t* x = (uint64_t*)(uintptr_t)x_qbsk;
+    // every word of conv that the second kernel reads is written by the first: nothing has to start at zero
+    CUDA_TRY(launch_basis_switch(z->floor->dev, conv, nb, 0, x, T, 0, batch, logN, false, s));
+    CUDA_TRY(launch_behz_floor(z->dev, x, conv, batch, logN, update_q != 0, s));
+    return FHE_OK;
+}
+
 extern "C" int fhe_fast_base_conv_sk(fhe_behz* z, fhe_dptr dst_q, fhe_dptr src_qbsk, size_t batch, int stream) {
     const char* who = "fhe_fast_base_conv_sk";
     StreamRef s;

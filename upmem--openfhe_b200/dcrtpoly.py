@@ -790,6 +790,10 @@ class Behz:
     def fast_rns_floor_q(self, x_qbsk, batch, update_q=True, stream=0):
         N.check(N.lib.fhe_fast_rns_floor_q(self.h, x_qbsk, batch, 1 if update_q else 0, stream))
 
+    def fast_rns_floor_q_noalloc(self, x_qbsk, batch, update_q=True, stream=0):
+        """Same result with the intermediate in the library's static 8 MiB device array: no allocation (fhe_b200.h)."""
+        N.check(N.lib.fhe_fast_rns_floor_q_noalloc(self.h, x_qbsk, batch, 1 if update_q else 0, stream))
+
     def fast_base_conv_sk(self, dst_q, src_qbsk, batch, stream=0):
         N.check(N.lib.fhe_fast_base_conv_sk(self.h, dst_q, src_qbsk, batch, stream))
 
