@@ -180,6 +180,35 @@ private:
   fhe_tower_scale *plan_ = nullptr;
 };
 
+/* The BEHZ set over a ring Q u Bsk (dcrtpoly-impl.h:2005-2050, 2069-2420; BFV multTech BEHZ): every table of
+ * bfvrns-cryptoparameters.cpp:724-891 derived from the moduli and the plaintext modulus t. */
+class PimBehz {
+public:
+  PimBehz(std::shared_ptr<PimRing> ring_qbsk, uint32_t size_q, uint64_t t) : ring_(std::move(ring_qbsk)), size_q_(size_q), t_(t) {
+    PimManager::check(fhe_behz_create(ring_->handle(), size_q, t, &plan_), "PimBehz");
+  }
+  ~PimBehz() { fhe_behz_destroy(plan_); }
+  PimBehz(const PimBehz &) = delete;
+  PimBehz &operator=(const PimBehz &) = delete;
+  fhe_behz *handle() const { return plan_; }
+  const std::shared_ptr<PimRing> &Ring() const { return ring_; }
+  uint32_t SizeQ() const { return size_q_; }
+  uint64_t PlaintextModulus() const { return t_; }
+  std::vector<uint64_t> Table(int which) const {       /* numbering of fhe_b200.h */
+    size_t n = 0;
+    PimManager::check(fhe_behz_table(plan_, which, nullptr, &n), "PimBehz::Table");
+    std::vector<uint64_t> v(n);
+    PimManager::check(fhe_behz_table(plan_, which, v.data(), nullptr), "PimBehz::Table");
+    return v;
+  }
+
+private:
+  std::shared_ptr<PimRing> ring_;
+  uint32_t size_q_;
+  uint64_t t_;
+  fhe_behz *plan_ = nullptr;
+};
+
 class PimDCRTPoly {
 public:
   PimDCRTPoly(std::shared_ptr<PimRing> ring, size_t batch, PimFormat format, const uint64_t *host = nullptr,

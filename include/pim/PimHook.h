@@ -774,6 +774,117 @@ inline bool resident_scale_round(PimManager *pim, const Towers &a, std::shared_p
   return true;
 }
 
+/* ---- BFV, BEHZ (dcrtpoly-impl.h:2069-2420) ------------------------------------------------------------------
+ * A plan over the ring Q u Bsk derives every table from the moduli and t.  FastBaseConvqToBskMontgomery and
+ * FastBaseConvSK do not receive t (their tables do not depend on it): they take any plan already cached for the ring,
+ * or build one with t = 2.  Each hook compares one of the caller's tables with the plan's own and leaves the call to
+ * the CPU statements when they differ, or when the device plan refuses the shape. */
+inline CachedPlan<PimBehz> behz_for(const std::shared_ptr<PimRing> &qbsk, uint32_t nq, uint64_t t) {
+  static std::mutex mu;
+  static std::map<std::tuple<PimRing *, uint32_t, int>, std::vector<CachedPlan<PimBehz>>> cache;
+  std::lock_guard<std::mutex> lock(mu);
+  auto &plans = cache[std::make_tuple(qbsk.get(), nq, hook_stream(qbsk->manager()->context()))];
+  for (auto &p : plans)
+    if (t == 0 || p.plan->PlaintextModulus() == t) return p;
+  CachedPlan<PimBehz> c;
+  try {
+    c.plan = std::make_shared<PimBehz>(qbsk, nq, t ? t : 2);
+  } catch (const std::exception &) {
+    return c;      /* no plan: the CPU path runs */
+  }
+  plans.push_back(c);
+  return c;
+}
+
+template <class IntVec>
+inline bool same_behz_table(const CachedPlan<PimBehz> &plan, int which, const IntVec &theirs) {
+  if (!plan.plan) return false;
+  const std::vector<uint64_t> mine = plan.plan->Table(which);
+  if (theirs.size() != mine.size()) return false;
+  for (size_t i = 0; i < mine.size(); i++)
+    if (mine[i] != theirs[i].ConvertToInt()) return false;
+  return true;
+}
+
+/* DCRTPolyImpl::FastBaseConvqToBskMontgomery (dcrtpoly-impl.h:2069-2209): a over Q (either format) -> out over QBsk,
+ * EVALUATION; `out` = host shells of the QBsk towers */
+template <class Towers, class IntVec>
+inline bool resident_behz_q_to_bsk(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
+                                   std::shared_ptr<Resident> &rout, int format, const IntVec &mtildeQHatInvModq) {
+  if (!pim || a.empty() || out.size() < a.size() + 2 || a[0].GetRingDimension() < 2) return false;
+  const int S = hook_stream(pim->context());
+  auto plan = behz_for(ring_of(pim, out), (uint32_t)a.size(), 0);
+  if (!same_behz_table(plan, 0, mtildeQHatInvModq)) return false;
+  auto da = ensure_device(pim, a, ra);
+  auto r = new_resident(pim, out);
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_fast_base_conv_q_to_bsk_montgomery(plan.plan->handle(), r->d, da->d, 1, format, S),
+                      "pim hook: FastBaseConvqToBskMontgomery");
+  }
+  finish(r->ctx);
+  rout = r;
+  return true;
+}
+
+/* DCRTPolyImpl::FastRNSFloorq (dcrtpoly-impl.h:2212-2271), in place on a over QBsk (nq = moduliQ.size()) */
+template <class Towers, class IntVec>
+inline bool resident_behz_floor(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, size_t nq, uint64_t t,
+                                const IntVec &tQHatInvModq) {
+  if (!pim || a.empty() || nq == 0 || a.size() < nq + 2 || a[0].GetRingDimension() < 2) return false;
+  const int S = hook_stream(pim->context());
+  auto plan = behz_for(ring_of(pim, a), (uint32_t)nq, t);
+  if (!same_behz_table(plan, 6, tQHatInvModq)) return false;
+  auto da = ensure_device(pim, a, ra);
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_fast_rns_floor_q(plan.plan->handle(), da->d, 1, 1, S), "pim hook: FastRNSFloorq");
+  }
+  finish(da->ctx);
+  std::lock_guard<std::mutex> lock(da->mu);
+  da->stream = S;
+  da->device_newer = true;
+  return true;
+}
+
+/* DCRTPolyImpl::FastBaseConvSK (dcrtpoly-impl.h:2309-2420): a over QBsk -> a new device copy over Q (its first nq
+ * towers); the caller then shrinks its host tower vector as the reference does (:2402-2408) */
+template <class Towers, class IntVec>
+inline bool resident_behz_conv_sk(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, size_t nq,
+                                  std::shared_ptr<Resident> &rout, const IntVec &BHatInvModb) {
+  if (!pim || a.empty() || nq == 0 || a.size() < nq + 2 || a[0].GetRingDimension() < 2) return false;
+  const int S = hook_stream(pim->context());
+  auto full = ring_of(pim, a);
+  auto plan = behz_for(full, (uint32_t)nq, 0);
+  if (!same_behz_table(plan, 9, BHatInvModb)) return false;
+  auto da = ensure_device(pim, a, ra);
+  static std::mutex mu;
+  static std::map<std::pair<PimRing *, size_t>, std::shared_ptr<PimRing>> views;      /* the Q towers of a QBsk ring */
+  std::shared_ptr<PimRing> rq;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto key = std::make_pair(full.get(), nq);
+    auto it = views.find(key);
+    if (it == views.end()) it = views.emplace(key, PimRing::View(full, 0, (uint32_t)nq)).first;
+    rq = it->second;
+  }
+  auto r = std::make_shared<Resident>();
+  r->ring = rq;
+  r->ctx = pim->context();
+  r->stream = S;
+  r->towers = nq;
+  r->n = da->n;
+  PimManager::check(fhe_alloc(r->ctx, r->towers * r->n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
+  r->device_newer = true;
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_fast_base_conv_sk(plan.plan->handle(), r->d, da->d, 1, S), "pim hook: FastBaseConvSK");
+  }
+  finish(r->ctx);
+  rout = r;
+  return true;
+}
+
 }  // namespace pimhook
 
 #endif /* _PIM_HOOK_ */

@@ -385,6 +385,50 @@ def patch_impl(text):
                 "            return dev;\n"
                 "        }\n"
                 "    }\n" + sig, rel)
+    # BEHZ: FastBaseConvqToBskMontgomery (in place, Q -> QBsk, EVALUATION), FastRNSFloorq (in place over QBsk),
+    # FastBaseConvSK (in place, QBsk -> Q)
+    sig = ("    const std::vector<NativeInteger>& mtildeInvModbskPrecon) {\n"
+           "    // Input: dcrtpoly in basis Q\n")
+    text = once(text, sig,
+                "    const std::vector<NativeInteger>& mtildeInvModbskPrecon) {\n"
+                "    if (pim && !m_vectors_.empty() && m_vectors_.size() == moduliQ.size() &&\n"
+                "        paramsQBsk->GetParams().size() == moduliQ.size() + moduliBsk.size()) {\n"
+                "        std::vector<DCRTPolyImpl::PolyType> shell;\n"
+                "        for (const auto& tp : paramsQBsk->GetParams()) shell.emplace_back(tp, Format::EVALUATION, false);\n"
+                "        std::shared_ptr<pimhook::Resident> up;\n"
+                "        if (pimhook::resident_behz_q_to_bsk(pim.get(), m_vectors_, pimres_, shell, up,\n"
+                "                                            m_format == Format::EVALUATION ? 0 : 1, mtildeQHatInvModq)) {\n"
+                "            m_vectors_ = std::move(shell);\n"
+                "            pimres_    = up;\n"
+                "            m_format   = Format::EVALUATION;\n"
+                "            m_params   = paramsQBsk;\n"
+                "            return;\n"
+                "        }\n"
+                "    }\n"
+                "    // Input: dcrtpoly in basis Q\n", rel)
+    sig = ("    const std::vector<NativeInteger>& tQInvModbskPrecon) {\n"
+           "    // Input: poly in basis {q U Bsk}\n")
+    text = once(text, sig,
+                "    const std::vector<NativeInteger>& tQInvModbskPrecon) {\n"
+                "    if (pim && m_vectors_.size() == moduliQ.size() + moduliBsk.size() &&\n"
+                "        pimhook::resident_behz_floor(pim.get(), m_vectors_, pimres_, moduliQ.size(), t.ConvertToInt(), tQHatInvModq))\n"
+                "        return;\n"
+                "    // Input: poly in basis {q U Bsk}\n", rel)
+    sig = ("    const std::vector<NativeInteger>& BModq, const std::vector<NativeInteger>& BModqPrecon) {\n"
+           "    // Input: poly in basis Bsk\n")
+    text = once(text, sig,
+                "    const std::vector<NativeInteger>& BModq, const std::vector<NativeInteger>& BModqPrecon) {\n"
+                "    if (pim && m_vectors_.size() == paramsQ->GetParams().size() + moduliBsk.size()) {\n"
+                "        const size_t devQ = paramsQ->GetParams().size();\n"
+                "        std::shared_ptr<pimhook::Resident> down;\n"
+                "        if (pimhook::resident_behz_conv_sk(pim.get(), m_vectors_, pimres_, devQ, down, BHatInvModb)) {\n"
+                "            m_vectors_.resize(devQ);\n"
+                "            pimres_  = down;\n"
+                "            m_params = paramsQ;\n"
+                "            return;\n"
+                "        }\n"
+                "    }\n"
+                "    // Input: poly in basis Bsk\n", rel)
     head, sep, tail = text.partition("namespace lbcrypto {")
     return head + "#define m_vectors PimHostVectors()\n" + sep + tail + "\n#undef m_vectors\n"
 

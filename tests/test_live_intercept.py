@@ -41,6 +41,12 @@ def load_hooked():
     H.ref_polys_approx_switch.restype = vp
     H.ref_polys_approx_switch.argtypes = [vp, vp]
     H.ref_set_table_tweak.argtypes = [ctypes.c_int]
+    H.ref_behz_create.restype = vp
+    H.ref_behz_create.argtypes = [vp, u32, u64]
+    H.ref_behz_destroy.argtypes = [vp]
+    H.ref_polys_behz_q_to_bsk.argtypes = [vp, vp]
+    H.ref_polys_behz_floor.argtypes = [vp, vp]
+    H.ref_polys_behz_conv_sk.argtypes = [vp, vp, vp]
     H.ref_polys_approx_mod_down.restype = vp
     H.ref_polys_approx_mod_down.argtypes = [vp, vp, vp, u64]
     H.ref_polys_approx_mod_up.argtypes = [vp, vp, vp]
@@ -260,6 +266,56 @@ def test_resident_neighbouring_methods(hooked, oracle, pkg):
         H.ref_polys_free(h)
     for c in (cQ, cP, cQP, cRest):
         H.ref_ctx_destroy(c)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_resident_behz_evalmult_core(hooked, oracle, pkg, fmt):
+    """BFV EvalMult with the BEHZ technique on the reference's own DCRTPoly with the handle attached
+    (bfvrns-leveledshe.cpp:275-297, 322-334, 367-388): FastBaseConvqToBskMontgomery of both operands, Times over QBsk,
+    SetFormat(COEFFICIENT), FastRNSFloorq, FastBaseConvSK.  Two uploads, nothing downloaded until the result is read,
+    and the result equals the oracle's (pinned against the CPU path of the same methods)."""
+    H = hooked
+    n, nq, t, batch = 1 << 11, 3, 65537, 2
+    T = 2 * nq + 1
+    q, psi = oracle.gen_params(55, n, T)
+    ob, octx = oracle.behz(n, q, psi, nq, t), oracle.ctx(n, q, psi)
+    cQBsk = H.ref_ctx_create(n, T, p(q), p(psi))
+    cQ = H.ref_ctx_create(n, nq, p(q[:nq].copy()), p(psi[:nq].copy()))
+    z = H.ref_behz_create(cQBsk, nq, t)
+    a, b = oracle.fill_ring(batch, n, q[:nq].copy(), 91), oracle.fill_ring(batch, n, q[:nq].copy(), 92)
+    ha, hb = H.ref_polys_load(cQ, p(a), batch, fmt), H.ref_polys_load(cQ, p(b), batch, fmt)
+    assert H.ref_polys_set_pim(ha, 1) == 0 and H.ref_polys_set_pim(hb, 1) == 0, H.ref_last_error()
+    up0, down0 = counters(H)
+    launches0 = pkg._native.lib.fhe_launch_count()
+    assert H.ref_polys_behz_q_to_bsk(ha, z) == 0, H.ref_last_error()
+    assert H.ref_polys_behz_q_to_bsk(hb, z) == 0, H.ref_last_error()
+    assert H.ref_polys_format(ha) == 0
+    assert H.ref_polys_op(ha, hb, 2, 1) >= 0                               # a *= b over QBsk
+    H.ref_polys_switch_format(ha, 1)                                       # -> COEFFICIENT
+    assert H.ref_polys_behz_floor(ha, z) == 0, H.ref_last_error()
+    assert H.ref_polys_behz_conv_sk(ha, z, cQ) == 0, H.ref_last_error()
+    assert counters(H) == (up0 + 2 * batch, down0), "nothing may be downloaded before the result is read"
+    assert pkg._native.lib.fhe_launch_count() - launches0 >= 8 * batch
+    res = np.empty((batch, nq, n), np.uint64)
+    H.ref_polys_store(ha, p(res))
+    prod = octx.elementwise(2, ob.q_to_bsk_montgomery(a, fmt), ob.q_to_bsk_montgomery(b, fmt))
+    want = ob.fast_base_conv_sk(ob.fast_rns_floor_q(octx.ntt(prod, inverse=True)))
+    assert np.array_equal(res, want)
+    assert counters(H) == (up0 + 2 * batch, down0 + batch)
+    # a caller with another plaintext modulus' tables gets what ITS tables say (a second plan for the same ring)
+    z2 = H.ref_behz_create(cQBsk, nq, 786433)
+    y = oracle.fill_ring(batch, n, q, 93)
+    hy = H.ref_polys_load(cQBsk, p(y), batch, 1)
+    assert H.ref_polys_set_pim(hy, 1) == 0
+    assert H.ref_polys_behz_floor(hy, z2) == 0, H.ref_last_error()
+    got = np.empty((batch, T, n), np.uint64)
+    H.ref_polys_store(hy, p(got))
+    assert np.array_equal(got, oracle.behz(n, q, psi, nq, 786433).fast_rns_floor_q(y))
+    for h in (ha, hb, hy):
+        H.ref_polys_free(h)
+    H.ref_behz_destroy(z); H.ref_behz_destroy(z2)
+    H.ref_ctx_destroy(cQBsk); H.ref_ctx_destroy(cQ)
 
 
 @pytest.mark.gpu
