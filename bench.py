@@ -772,6 +772,18 @@ def ntt_extra(pkg, be):
             "note": "ExpandCRTBasis x2 + (INTT, FastExpandCRTBasisPloverQ, NTT) x2 -> tensor product over QR -> INTT -> "
                     "ScaleAndRound to Q, device-resident"}
         mult.close()
+        ring.close()
+        # the same product with the BEHZ technique (bfvrns-leveledshe.cpp:275-297, 367-388): Bsk = 16 towers of B and msk;
+        # 4 FastBaseConvqToBskMontgomery, tensor product over QBsk, 3 x (INTT, FastRNSFloorq, FastBaseConvSK)
+        q, psi = pkg.gen_params(60, n, 2 * sq + 1)
+        ring = pkg.Ring(be, n, q, psi)
+        mult = pkg.BfvBehzMult(ring, sq, 65537)
+        ms = timed(lambda: mult(outs, ins[0:2], ins[2:4], batch), reps=3)
+        out["bfv_behz_evalmult_core_n32768_q16_bsk17_b32"] = {
+            "ms": ms, "ciphertext_products_per_s": batch / (ms * 1e-3),
+            "note": "FastBaseConvqToBskMontgomery x4 -> tensor product over QBsk -> INTT -> FastRNSFloorq -> FastBaseConvSK, "
+                    "device-resident"}
+        mult.close()
         for p_ in ins + outs:
             be.free(p_)
         ring.close()
