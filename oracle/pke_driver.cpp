@@ -1,0 +1,209 @@
+// pke_driver.cpp — the reference's OWN scheme layer (src/pke: BFV / BGV / CKKS) run on top of the hooked DCRTPoly
+// (TEST INFRASTRUCTURE ONLY).  Compiled by `make -C oracle pke` with the reference's sources where they lie and
+// -DFIXED_SEED (math/distributiongenerator.h:51), so the PRNG stream is the same in every run on one thread.
+//
+// Every scenario prints one line per ciphertext / plaintext: a name and a digest of every tower word.  Run once with
+// FHE_B200_ATTACH=1 (every DCRTPoly the schemes create carries the backend handle: their +, *, SwitchFormat, automorphisms,
+// basis conversions, rescaling and the BEHZ set run on the GPU, pim/PimHook.h) and once without (the reference's CPU
+// statements): the two outputs must be identical, which tests/test_pke_under_hook.py checks.  Nothing here restates
+// arithmetic.
+#include "openfhe.h"
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+#include <vector>
+
+#include "fhe_b200.h"
+
+using namespace lbcrypto;
+
+static uint64_t digest_poly(const DCRTPoly& poly, uint64_t h) {
+    for (const auto& tower : poly.GetAllElements()) {        // reads the host towers: a device copy is downloaded first
+        const auto& v = tower.GetValues();
+        for (usint i = 0; i < v.GetLength(); i++) {
+            h ^= v[i].ConvertToInt();
+            h *= 0x100000001B3ull;                           // FNV-1a over 64-bit words
+        }
+        h ^= tower.GetModulus().ConvertToInt();
+        h *= 0x100000001B3ull;
+    }
+    h ^= (uint64_t)poly.GetFormat() + 17;
+    return h * 0x100000001B3ull;
+}
+static void show(const std::string& name, ConstCiphertext<DCRTPoly> ct) {
+    uint64_t h = 0xcbf29ce484222325ull;
+    for (const auto& e : ct->GetElements()) h = digest_poly(e, h);
+    std::printf("%s ct elements=%zu towers=%zu digest=%016llx\n", name.c_str(), ct->GetElements().size(),
+                (size_t)ct->GetElements()[0].GetNumOfElements(), (unsigned long long)h);
+}
+static void show(const std::string& name, const std::vector<int64_t>& v) {
+    std::printf("%s pt", name.c_str());
+    for (auto x : v) std::printf(" %lld", (long long)x);
+    std::printf("\n");
+}
+static void show(const std::string& name, const std::vector<double>& v) {
+    std::printf("%s pt", name.c_str());
+    for (auto x : v) std::printf(" %.6f", x);
+    std::printf("\n");
+}
+
+struct Clock {
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    double ms() const { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); }
+};
+
+static const std::vector<int64_t> V1 = {1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12};
+static const std::vector<int64_t> V2 = {3, 2, 1, 4, 5, 6, 7, 8, 9, 10, 11, 12};
+
+// BFVrns: KeyGen, Encrypt, EvalAdd, EvalMult + relinearisation (twice: depth 2), EvalRotate, Decrypt
+static void run_bfv(const char* label, MultiplicationTechnique tech, KeySwitchTechnique ks, uint32_t ringDim) {
+    Clock clk;
+    CCParams<CryptoContextBFVRNS> P;
+    P.SetPlaintextModulus(65537);
+    P.SetMultiplicativeDepth(2);
+    P.SetMultiplicationTechnique(tech);
+    P.SetKeySwitchTechnique(ks);
+    P.SetSecurityLevel(HEStd_NotSet);
+    P.SetRingDim(ringDim);
+    CryptoContext<DCRTPoly> cc = GenCryptoContext(P);
+    cc->Enable(PKE);
+    cc->Enable(KEYSWITCH);
+    cc->Enable(LEVELEDSHE);
+    auto kp = cc->KeyGen();
+    cc->EvalMultKeyGen(kp.secretKey);
+    cc->EvalRotateKeyGen(kp.secretKey, {1, -2});
+    auto c1 = cc->Encrypt(kp.publicKey, cc->MakePackedPlaintext(V1));
+    auto c2 = cc->Encrypt(kp.publicKey, cc->MakePackedPlaintext(V2));
+    const std::string L(label);
+    show(L + ".c1", c1);
+    auto cadd = cc->EvalAdd(c1, c2);
+    show(L + ".add", cadd);
+    auto csub = cc->EvalSub(c1, c2);
+    show(L + ".sub", csub);
+    auto cmul = cc->EvalMult(c1, c2);
+    show(L + ".mul", cmul);
+    auto cmul2 = cc->EvalMult(cmul, cadd);
+    show(L + ".mul2", cmul2);
+    auto crot = cc->EvalRotate(cmul, 1);
+    show(L + ".rot1", crot);
+    auto crot2 = cc->EvalRotate(cadd, -2);
+    show(L + ".rot-2", crot2);
+    for (auto& item : std::vector<std::pair<std::string, Ciphertext<DCRTPoly>>>{
+             {"add", cadd}, {"sub", csub}, {"mul", cmul}, {"mul2", cmul2}, {"rot1", crot}, {"rot-2", crot2}}) {
+        Plaintext r;
+        cc->Decrypt(kp.secretKey, item.second, &r);
+        r->SetLength(V1.size());
+        show(L + ".dec." + item.first, r->GetPackedValue());
+    }
+    std::fprintf(stderr, "%s: %.1f ms, launches so far %ld\n", label, clk.ms(), fhe_launch_count());
+}
+
+// BGVrns: EvalMult, ModReduce (explicit with FIXEDMANUAL), EvalRotate
+static void run_bgv(const char* label, ScalingTechnique st, uint32_t ringDim) {
+    Clock clk;
+    CCParams<CryptoContextBGVRNS> P;
+    P.SetPlaintextModulus(65537);
+    P.SetMultiplicativeDepth(2);
+    P.SetScalingTechnique(st);
+    P.SetSecurityLevel(HEStd_NotSet);
+    P.SetRingDim(ringDim);
+    CryptoContext<DCRTPoly> cc = GenCryptoContext(P);
+    cc->Enable(PKE);
+    cc->Enable(KEYSWITCH);
+    cc->Enable(LEVELEDSHE);
+    auto kp = cc->KeyGen();
+    cc->EvalMultKeyGen(kp.secretKey);
+    cc->EvalRotateKeyGen(kp.secretKey, {1});
+    auto c1 = cc->Encrypt(kp.publicKey, cc->MakePackedPlaintext(V1));
+    auto c2 = cc->Encrypt(kp.publicKey, cc->MakePackedPlaintext(V2));
+    const std::string L(label);
+    auto cadd = cc->EvalAdd(c1, c2);
+    show(L + ".add", cadd);
+    auto cmul = cc->EvalMult(c1, c2);
+    show(L + ".mul", cmul);
+    if (st == FIXEDMANUAL) {
+        cmul = cc->ModReduce(cmul);
+        show(L + ".modreduce", cmul);
+    }
+    auto cmul2 = cc->EvalMult(cmul, cmul);
+    show(L + ".mul2", cmul2);
+    auto crot = cc->EvalRotate(cmul, 1);
+    show(L + ".rot1", crot);
+    for (auto& item : std::vector<std::pair<std::string, Ciphertext<DCRTPoly>>>{{"add", cadd}, {"mul", cmul}, {"mul2", cmul2}, {"rot1", crot}}) {
+        Plaintext r;
+        cc->Decrypt(kp.secretKey, item.second, &r);
+        r->SetLength(V1.size());
+        show(L + ".dec." + item.first, r->GetPackedValue());
+    }
+    std::fprintf(stderr, "%s: %.1f ms, launches so far %ld\n", label, clk.ms(), fhe_launch_count());
+}
+
+// CKKSrns: EvalMult, Rescale, EvalAdd, plaintext multiplication, EvalRotate (hybrid key switching: ApproxModUp / ApproxModDown)
+static void run_ckks(const char* label, ScalingTechnique st, KeySwitchTechnique ks, uint32_t ringDim) {
+    Clock clk;
+    CCParams<CryptoContextCKKSRNS> P;
+    P.SetMultiplicativeDepth(3);
+    P.SetScalingModSize(50);
+    P.SetBatchSize(8);
+    P.SetScalingTechnique(st);
+    P.SetKeySwitchTechnique(ks);
+    if (ks == BV) P.SetDigitSize(10);
+    P.SetSecurityLevel(HEStd_NotSet);
+    P.SetRingDim(ringDim);
+    CryptoContext<DCRTPoly> cc = GenCryptoContext(P);
+    cc->Enable(PKE);
+    cc->Enable(KEYSWITCH);
+    cc->Enable(LEVELEDSHE);
+    auto kp = cc->KeyGen();
+    cc->EvalMultKeyGen(kp.secretKey);
+    cc->EvalRotateKeyGen(kp.secretKey, {1, -2});
+    const std::vector<double> x1 = {0.25, 0.5, 0.75, 1.0, 2.0, 3.0, 4.0, 5.0}, x2 = {5.0, 4.0, 3.0, 2.0, 1.0, 0.75, 0.5, 0.25};
+    auto p1 = cc->MakeCKKSPackedPlaintext(x1), p2 = cc->MakeCKKSPackedPlaintext(x2);
+    auto c1 = cc->Encrypt(kp.publicKey, p1), c2 = cc->Encrypt(kp.publicKey, p2);
+    const std::string L(label);
+    auto cadd = cc->EvalAdd(c1, c2);
+    show(L + ".add", cadd);
+    auto cmul = cc->EvalMult(c1, c2);
+    show(L + ".mul", cmul);
+    if (st == FIXEDMANUAL) {
+        cmul = cc->Rescale(cmul);
+        show(L + ".rescale", cmul);
+    }
+    auto cpt = cc->EvalMult(cmul, p1);
+    if (st == FIXEDMANUAL) cpt = cc->Rescale(cpt);
+    show(L + ".mulpt", cpt);
+    auto csq = cc->EvalMult(cmul, cmul);
+    if (st == FIXEDMANUAL) csq = cc->Rescale(csq);
+    show(L + ".square", csq);
+    auto crot = cc->EvalRotate(cmul, 1);
+    show(L + ".rot1", crot);
+    auto crot2 = cc->EvalRotate(c1, -2);
+    show(L + ".rot-2", crot2);
+    for (auto& item : std::vector<std::pair<std::string, Ciphertext<DCRTPoly>>>{
+             {"add", cadd}, {"mul", cmul}, {"mulpt", cpt}, {"square", csq}, {"rot1", crot}, {"rot-2", crot2}}) {
+        Plaintext r;
+        cc->Decrypt(kp.secretKey, item.second, &r);
+        r->SetLength(8);
+        show(L + ".dec." + item.first, r->GetRealPackedValue());
+    }
+    std::fprintf(stderr, "%s: %.1f ms, launches so far %ld\n", label, clk.ms(), fhe_launch_count());
+}
+
+int main(int argc, char** argv) {
+    const uint32_t n = argc > 1 ? (uint32_t)std::atoi(argv[1]) : 4096;
+    const std::string only = argc > 2 ? argv[2] : "";
+    auto want = [&](const char* s) { return only.empty() || only == s; };
+    if (want("bfv-hps")) run_bfv("bfv-hps", HPS, HYBRID, n);
+    if (want("bfv-hpspoverq")) run_bfv("bfv-hpspoverq", HPSPOVERQ, HYBRID, n);
+    if (want("bfv-hpspoverqleveled")) run_bfv("bfv-hpspoverqleveled", HPSPOVERQLEVELED, HYBRID, n);
+    if (want("bfv-behz")) run_bfv("bfv-behz", BEHZ, BV, n);
+    if (want("bgv-manual")) run_bgv("bgv-manual", FIXEDMANUAL, n);
+    if (want("bgv-auto")) run_bgv("bgv-auto", FLEXIBLEAUTO, n);
+    if (want("ckks-manual")) run_ckks("ckks-manual", FIXEDMANUAL, HYBRID, n);
+    if (want("ckks-auto")) run_ckks("ckks-auto", FLEXIBLEAUTO, HYBRID, n);
+    if (want("ckks-bv")) run_ckks("ckks-bv", FIXEDMANUAL, BV, n);
+    std::fprintf(stderr, "total kernel launches %ld\n", fhe_launch_count());
+    return 0;
+}
