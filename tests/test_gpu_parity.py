@@ -518,6 +518,34 @@ def test_ntt_ws_kernels_vs_oracle(pkg, backend, oracle, logn, towers, batch, nbi
     ring.close()
 
 
+@pytest.mark.parametrize("logn,towers,batch,nbits", [(12, 3, 5, 60), (13, 2, 9, 45), (14, 3, 8, 60), (15, 2, 64, 33), (16, 2, 7, 60), (16, 30, 8, 60)])
+def test_ntt_prefetching_strided_pass_vs_oracle(pkg, backend, oracle, monkeypatch, logn, towers, batch, nbits):
+    """The persistent strided pass with register prefetch (ntt_strided_pf_kernel, FHE_B200_NTT_PF=2 forces it; off by
+    default): CTAs walk over several tiles (more tiles than CTAs at the larger shapes), both directions."""
+    monkeypatch.setenv("FHE_B200_NTT_PF", "2")
+    n = 1 << logn
+    q, psi = params(oracle, nbits, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q, psi)
+    rng = np.random.default_rng(700 + logn * 31 + batch)
+    x = rand_polys(rng, batch, n, q)
+    x[0, :, 0] = (q - 1)
+    x[0, 0, :] = q[0] - 1
+    words = ring.words(batch)
+    d = backend.alloc(words * 8)
+    backend.h2d(d, x)
+    ring.ntt(d, batch, False, algo=2)
+    assert np.array_equal(backend.d2h(d, words).reshape(x.shape), octx.ntt(x, inverse=False)), "forward"
+    ring.ntt(d, batch, True, algo=2)
+    assert np.array_equal(backend.d2h(d, words).reshape(x.shape), x), "round trip"
+    y = rand_polys(rng, batch, n, q)
+    backend.h2d(d, y)
+    ring.ntt(d, batch, True, algo=2)
+    assert np.array_equal(backend.d2h(d, words).reshape(x.shape), octx.ntt(y, inverse=True)), "inverse"
+    backend.free(d)
+    ring.close()
+
+
 def test_ntt_ws_full_size_round_trip_property(pkg, backend, oracle):
     """BASELINE configs[2] ring at a batch the default dispatch sends to the persistent kernels: forward then inverse
     is the identity, and the forward result equals the one-tile-per-CTA kernels' (which the oracle pins at small batch)."""

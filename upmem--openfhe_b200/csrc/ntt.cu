@@ -148,6 +148,114 @@ ntt_strided_kernel(u64* __restrict__ data, const u64* __restrict__ in, const ulo
 }
 
 // ------------------------------------------------------------------------------------------
+// The strided pass as a persistent kernel with register prefetch (round 2).  ncu's stall sampling of the one-tile kernel
+// above shows its idle issue cycles are mostly warps waiting for the tile's first loads (long scoreboard on the first
+// butterflies of the tile).  Here a CTA walks over tiles and issues the loads of its NEXT tile into the registers that the
+// current tile has just left (its values are in shared memory by then), so they fly while the second half of the current
+// tile is computed.  The exchange buffer is double-buffered: one barrier per tile.  Same arithmetic, same tile shape.
+// Needs A = 4 (RL >= 4), i.e. one register group per thread in the first step.
+// ------------------------------------------------------------------------------------------
+template <int RL, int TL, bool INV>
+__global__ void __launch_bounds__(StridedCfg<RL, TL>::THREADS)
+ntt_strided_pf_kernel(u64* __restrict__ data, const u64* __restrict__ in, const ulonglong2* __restrict__ twAll,
+                      const TowerMod* __restrict__ mods, const ulonglong2* __restrict__ invc,
+                      u32 T, u32 logN, u32 outT, u32 inT, u32 ntiles) {
+    using K = StridedCfg<RL, TL>;
+    static_assert(K::A == 4 && K::B >= 1 && K::GA == 1, "prefetch form: 16 coefficients per thread in the first step");
+    auto sidx = [](u32 row, u32 c) -> u32 { return row * K::C + c + (row >> K::B) * K::PAD; };
+    extern __shared__ __align__(16) u64 small[];
+    constexpr int A = K::A, B = K::B, C = K::C;
+    constexpr u32 tilesPerUnit = 256 / C;
+    constexpr u32 SMW = K::SMEM / 8;
+    const u32 tid = threadIdx.x;
+    // the thread's place in the tile, for the step that touches global memory first (forward: A; inverse: B)
+    const u32 cA = tid % C, ulow = tid / C;
+
+    struct Tile { u32 tower; size_t ioff, ooff; };
+    auto decode = [&](u32 L) -> Tile {
+        const u32 cg = L % tilesPerUnit, rest = L / tilesPerUnit;
+        const u32 tower = rest % T, bitem = rest / T;
+        Tile t;
+        t.tower = tower;
+        t.ooff = (((size_t)bitem * outT + tower) << logN) + cg * C;
+        t.ioff = (((size_t)bitem * inT + tower) << logN) + cg * C;
+        return t;
+    };
+    // the 16 coefficients this thread reads from global memory for a tile
+    auto load = [&](u64 (&x)[16], const Tile& t) {
+        const u64* ibase = in + t.ioff;
+        if (!INV) {
+#pragma unroll
+            for (int e = 0; e < 16; e++) x[e] = ibase[((size_t)((e << B) + ulow) << 8) + cA];
+        } else {
+#pragma unroll
+            for (int g = 0; g < K::GB; g++) {
+                const u32 item = tid + g * K::THREADS, c = item % C, uhi = item / C;
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) x[g * (1 << B) + e] = ibase[((size_t)((uhi << B) + e) << 8) + c];
+            }
+        }
+    };
+
+    u32 L = blockIdx.x;
+    if (L >= ntiles) return;
+    Tile cur = decode(L);
+    u64 x[16];
+    load(x, cur);
+    for (u32 it = 0;; it++) {
+        u64* sm = small + (it & 1u) * SMW;
+        const u32 Ln = L + gridDim.x;
+        const bool more = Ln < ntiles;
+        Tile nxt = cur;
+        if (more) nxt = decode(Ln);
+        const u64 q = mods[cur.tower].q, nq = 0ull - q;
+        const QMul Q = make_qmul(q);
+        const ulonglong2* tw = twAll + ((size_t)cur.tower << logN);
+        u64* base = data + cur.ooff;
+        if (!INV) {
+            fwd_step<A, 1>(x, tw, 1u, Q, nq);
+#pragma unroll
+            for (int e = 0; e < 16; e++) sm[sidx((e << B) + ulow, cA)] = x[e];
+            if (more) load(x, nxt);                 // x is free: the next tile's loads fly during the second step
+            __syncthreads();
+#pragma unroll
+            for (int g = 0; g < K::GB; g++) {
+                const u32 item = tid + g * K::THREADS, c = item % C, uhi = item / C;
+                u64 y[1 << B];
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) y[e] = sm[sidx((uhi << B) + e, c)];
+                fwd_step<B, FwdStep<A, 1>::OUT>(y, tw, (1u << A) + uhi, Q, nq);
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) base[((size_t)((uhi << B) + e) << 8) + c] = y[e];
+            }
+        } else {
+            const ulonglong2 sc = invc[2 * cur.tower], w1 = invc[2 * cur.tower + 1];
+#pragma unroll
+            for (int g = 0; g < K::GB; g++) {
+                const u32 item = tid + g * K::THREADS, c = item % C, uhi = item / C;
+                u64 y[1 << B];
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) y[e] = x[g * (1 << B) + e];
+                inv_step<B, INV_NORM, INV_NORM>(y, tw, (1u << A) + uhi, Q, nq);
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) sm[sidx((uhi << B) + e, c)] = y[e];
+            }
+            if (more) load(x, nxt);
+            __syncthreads();
+            u64 y[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) y[e] = sm[sidx((e << B) + ulow, cA)];
+            inv_step_last<A, INV_NORM>(y, tw, sc, w1, Q, nq);
+#pragma unroll
+            for (int e = 0; e < 16; e++) base[((size_t)((e << B) + ulow) << 8) + cA] = y[e];
+        }
+        if (!more) break;
+        L = Ln;
+        cur = nxt;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // Contig pass: 256-point sub-NTTs over contiguous blocks (transform stages L-8..L-1).
 // Tile = NC = 2^LB sub-NTTs (16, 8 or 4): CB batch items x CH consecutive blocks (CB*CH = NC),
 // 16*NC threads.  Shared layout [u][c] with the column XOR-swizzled by bits of u (and, for NC < 16, NC
@@ -334,6 +442,12 @@ static int tile_log(int which) {
     return tl[which];
 }
 
+// FHE_B200_NTT_PF: 0 one-tile kernels, 1 the persistent prefetching strided kernel for large batches, 2 always (tests)
+static int ntt_pf_mode() {
+    const char* e = getenv("FHE_B200_NTT_PF");        // read every time: the tests switch it
+    return e && *e ? atoi(e) : NTT_PF_DEFAULT;
+}
+
 template <int RL, int TL, bool INV>
 static cudaError_t launch_strided_t(const RingDev& r, u64* data, const u64* in, u32 outT, u32 inT, size_t batch, cudaStream_t st) {
     using K = StridedCfg<RL, TL>;
@@ -356,6 +470,30 @@ static cudaError_t launch_strided_t(const RingDev& r, u64* data, const u64* in, 
         by /= d; bz *= d;
     }
     if (bz > 65535u) return cudaErrorInvalidValue;
+    if constexpr (K::A == 4 && K::B >= 1) {
+        const size_t ntiles = (size_t)r.T * (256 / K::C) * batch;
+        if (ntt_pf_mode() != 0 && ntiles < 0x7fffffffull && (ntt_pf_mode() == 2 || ntiles >= 148 * 64)) {
+            static std::atomic<int> occ_cache{0};
+            int occ = occ_cache.load(std::memory_order_relaxed);
+            if (occ == 0) {
+                if (2 * K::SMEM > 48 * 1024) {
+                    cudaError_t e = cudaFuncSetAttribute(ntt_strided_pf_kernel<RL, TL, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * K::SMEM);
+                    if (e != cudaSuccess) return e;
+                }
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ntt_strided_pf_kernel<RL, TL, INV>, K::THREADS, 2 * K::SMEM) != cudaSuccess || occ < 1) occ = 1;
+                occ_cache.store(occ, std::memory_order_relaxed);
+            }
+            int dev = 0, sms = 148;
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            size_t g = (size_t)sms * occ;
+            if (g > ntiles) g = ntiles;
+            ntt_strided_pf_kernel<RL, TL, INV><<<(unsigned)g, K::THREADS, 2 * K::SMEM, st>>>(
+                data, in, INV ? r.twI : r.twF, r.mods, r.invc, r.T, r.logN, outT, inT, (u32)ntiles);
+            kernel_launch_count_add(1);
+            return cudaGetLastError();
+        }
+    }
     dim3 grid(r.T * (256 / K::C), by, bz);
     ntt_strided_kernel<RL, TL, INV><<<grid, K::THREADS, K::SMEM, st>>>(
         data, in, INV ? r.twI : r.twF, r.mods, r.invc, r.T, r.logN, outT, inT);
