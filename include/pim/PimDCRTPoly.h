@@ -180,6 +180,25 @@ private:
   fhe_tower_scale *plan_ = nullptr;
 };
 
+/* Hybrid key switching over a ring Ql u P (KeySwitchHYBRID::KeySwitchCore, src/pke/lib/keyswitch/keyswitch-hybrid.cpp:
+ * 324-480): digit tables over the (possibly truncated) partitions of Ql and the ModDown tables, derived from the moduli. */
+class PimKeySwitch {
+public:
+  PimKeySwitch(std::shared_ptr<PimRing> ring_qlp, uint32_t size_ql, uint32_t alpha) : ring_(std::move(ring_qlp)) {
+    PimManager::check(fhe_keyswitch_create(ring_->handle(), size_ql, alpha, &plan_), "PimKeySwitch");
+  }
+  ~PimKeySwitch() { fhe_keyswitch_destroy(plan_); }
+  PimKeySwitch(const PimKeySwitch &) = delete;
+  PimKeySwitch &operator=(const PimKeySwitch &) = delete;
+  fhe_keyswitch *handle() const { return plan_; }
+  uint32_t Digits() const { return fhe_keyswitch_digits(plan_); }
+  const std::shared_ptr<PimRing> &Ring() const { return ring_; }
+
+private:
+  std::shared_ptr<PimRing> ring_;
+  fhe_keyswitch *plan_ = nullptr;
+};
+
 /* The BEHZ set over a ring Q u Bsk (dcrtpoly-impl.h:2005-2050, 2069-2420; BFV multTech BEHZ): every table of
  * bfvrns-cryptoparameters.cpp:724-891 derived from the moduli and the plaintext modulus t. */
 class PimBehz {

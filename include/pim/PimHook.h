@@ -885,6 +885,122 @@ inline bool resident_behz_conv_sk(PimManager *pim, const Towers &a, std::shared_
   return true;
 }
 
+/* ---- ciphertext level: KeySwitchHYBRID::KeySwitchCore (src/pke/lib/keyswitch/keyswitch-hybrid.cpp:324-480) ------------
+ * The reference builds the digits tower by tower on the host (SetElementAtIndex), runs the inner product with the key on
+ * NativePolys and only the basis conversions on DCRTPolys, so with the per-polynomial hooks alone a key switch bounces
+ * between host and device.  Here the whole of EvalKeySwitchPrecomputeCore + EvalFastKeySwitchCoreExt + the two ApproxModDown
+ * is ONE device composition (fhe_keyswitch_hybrid) on the resident ciphertext element and a device copy of the key:
+ * the key's towers that the level uses (the first sizeQl and the sizeP towers of P, :462-478) are gathered once per
+ * (key, level) into [digits][Ql u P][N] blocks, HBM to HBM, and kept. */
+inline CachedPlan<PimKeySwitch> keyswitch_for(const std::shared_ptr<PimRing> &qlp, uint32_t size_ql, uint32_t alpha) {
+  static std::mutex mu;
+  static std::map<std::tuple<PimRing *, uint32_t, uint32_t, int>, CachedPlan<PimKeySwitch>> cache;
+  std::lock_guard<std::mutex> lock(mu);
+  auto key = std::make_tuple(qlp.get(), size_ql, alpha, hook_stream(qlp->manager()->context()));
+  auto it = cache.find(key);
+  if (it != cache.end()) return it->second;
+  CachedPlan<PimKeySwitch> c;
+  c.plan = std::make_shared<PimKeySwitch>(qlp, size_ql, alpha);
+  cache.emplace(key, c);
+  return c;
+}
+
+template <class Towers>
+struct KeyRef {
+  const Towers &towers;
+  std::shared_ptr<Resident> &res;
+};
+
+struct KeyBlock {          /* evk_b, evk_a as fhe_keyswitch_inner reads them: [digits][sizeQl + sizeP][N] each */
+  fhe_ctx *ctx = nullptr;
+  fhe_dptr b = 0, a = 0, from = 0;
+  size_t bytes = 0;
+  ~KeyBlock() {
+    if (b) fhe_free(ctx, b);
+    if (a) fhe_free(ctx, a);
+  }
+};
+
+template <class Towers, class KeyAt>
+inline bool resident_keyswitch_hybrid(PimManager *pim, const Towers &c, std::shared_ptr<Resident> &rc, size_t nkeys, KeyAt key_at,
+                                      size_t sizeP, size_t alpha, uint64_t t, const void *key_id, std::shared_ptr<Resident> &r0,
+                                      std::shared_ptr<Resident> &r1) {
+  if (!pim || c.empty() || sizeP == 0 || alpha == 0 || nkeys == 0) return false;
+  const size_t sizeQl = c.size(), np = (sizeQl + alpha - 1) / alpha, T = sizeQl + sizeP, n = c[0].GetRingDimension();
+  if (np > nkeys || n < 2) return false;
+  KeyRef<Towers> k0 = key_at(0, 0);
+  if (k0.towers.size() < T) return false;
+  const size_t sizeQ = k0.towers.size() - sizeP;
+  for (size_t i = 0; i < sizeQl; i++)
+    if (k0.towers[i].GetModulus() != c[i].GetModulus()) return false;      /* not the key's own chain of moduli: CPU path */
+  std::vector<uint64_t> q, psi;
+  for (size_t i = 0; i < sizeQl; i++) { q.push_back(c[i].GetModulus().ConvertToInt()); psi.push_back(c[i].GetRootOfUnity().ConvertToInt()); }
+  for (size_t i = sizeQ; i < sizeQ + sizeP; i++) {
+    q.push_back(k0.towers[i].GetModulus().ConvertToInt());
+    psi.push_back(k0.towers[i].GetRootOfUnity().ConvertToInt());
+  }
+  auto ring = ring_for(pim, (uint32_t)n, q, psi);
+  fhe_ctx *ctx = pim->context();
+  const int S = hook_stream(ctx);
+  auto plan = keyswitch_for(ring, (uint32_t)sizeQl, (uint32_t)alpha);
+  /* the key's device block for this level */
+  static std::mutex mu;
+  static std::map<std::tuple<const void *, size_t, fhe_ctx *>, std::shared_ptr<KeyBlock>> keys;
+  static size_t held = 0;
+  std::shared_ptr<KeyBlock> kb;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto d0 = ensure_device(pim, k0.towers, k0.res);
+    auto id = std::make_tuple(key_id, sizeQl, ctx);
+    auto it = keys.find(id);
+    if (it != keys.end() && it->second->from == d0->d) {
+      kb = it->second;
+    } else {
+      const size_t tower = n * sizeof(uint64_t), bytes = np * T * tower;
+      if (held + 2 * bytes > ((size_t)16 << 30)) { keys.clear(); held = 0; }      /* bounded: blocks in use live on through their shared_ptr */
+      kb = std::make_shared<KeyBlock>();
+      kb->ctx = ctx;
+      kb->from = d0->d;
+      kb->bytes = 2 * bytes;
+      PimManager::check(fhe_alloc(ctx, bytes, &kb->b), "pim hook: key block");
+      PimManager::check(fhe_alloc(ctx, bytes, &kb->a), "pim hook: key block");
+      for (int which = 0; which < 2; which++)
+        for (size_t j = 0; j < np; j++) {
+          KeyRef<Towers> kr = key_at(which, j);
+          if (kr.towers.size() != sizeQ + sizeP) return false;
+          auto dk = ensure_device(pim, kr.towers, kr.res);
+          const fhe_dptr dst = (which ? kb->a : kb->b) + j * T * tower;
+          PimManager::check(fhe_d2d(ctx, dst, dk->d, sizeQl * tower, S), "pim hook: key gather");
+          PimManager::check(fhe_d2d(ctx, dst + sizeQl * tower, dk->d + sizeQ * tower, sizeP * tower, S), "pim hook: key gather");
+        }
+      PimManager::check(fhe_sync(ctx, S), "pim hook: key gather");      /* other threads use the block on their own streams */
+      keys[id] = kb;
+      held += 2 * bytes;
+    }
+  }
+  auto da = ensure_device(pim, c, rc);
+  auto fresh = [&] {
+    auto r = std::make_shared<Resident>();
+    r->ring = da->ring;
+    r->ctx = ctx;
+    r->stream = S;
+    r->towers = sizeQl;
+    r->n = n;
+    PimManager::check(fhe_alloc(ctx, sizeQl * n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
+    r->device_newer = true;
+    return r;
+  };
+  auto o0 = fresh(), o1 = fresh();
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_keyswitch_hybrid(plan.plan->handle(), o0->d, o1->d, da->d, kb->b, kb->a, 1, t, S), "pim hook: hybrid key switch");
+  }
+  finish(ctx);
+  r0 = o0;
+  r1 = o1;
+  return true;
+}
+
 }  // namespace pimhook
 
 #endif /* _PIM_HOOK_ */

@@ -113,6 +113,32 @@ def patch_class(text):
     text = once(text, "        m_format  = rhs.m_format;\n        m_vectors = rhs.m_vectors;\n        return *this;\n",
                 "        m_format  = rhs.m_format;\n        PimCopyFrom(rhs);\n"
                 "        if (rhs.pim) pim = rhs.pim;\n        return *this;\n", rel)
+    # ciphertext level: KeySwitchHYBRID::KeySwitchCore as one device composition (pim/PimHook.h resident_keyswitch_hybrid);
+    # a static member, because it reaches into the key's polynomials
+    text = once(text, "    std::shared_ptr<PimManager> GetPim() {\n        return pim;\n    }\n",
+                "    std::shared_ptr<PimManager> GetPim() {\n        return pim;\n    }\n\n"
+                "    static bool PimKeySwitchHybrid(const DCRTPolyImpl& c, const std::vector<DCRTPolyImpl>& bv,\n"
+                "                                   const std::vector<DCRTPolyImpl>& av, size_t sizeP, size_t alpha, uint64_t t,\n"
+                "                                   const void* keyId, DCRTPolyImpl& ct0, DCRTPolyImpl& ct1) {\n"
+                "        if (!c.pim || c.m_format != Format::EVALUATION || bv.empty() || bv.size() != av.size()) return false;\n"
+                "        for (size_t j = 0; j < bv.size(); j++)\n"
+                "            if (bv[j].m_format != Format::EVALUATION || av[j].m_format != Format::EVALUATION) return false;\n"
+                "        using Towers = std::vector<PolyType>;\n"
+                "        auto keyAt = [&](int which, size_t j) {\n"
+                "            const DCRTPolyImpl& k = which ? av[j] : bv[j];\n"
+                "            return pimhook::KeyRef<Towers>{k.m_vectors_, k.pimres_};\n"
+                "        };\n"
+                "        std::shared_ptr<pimhook::Resident> r0, r1;\n"
+                "        if (!pimhook::resident_keyswitch_hybrid(c.pim.get(), c.m_vectors_, c.pimres_, bv.size(), keyAt, sizeP, alpha, t,\n"
+                "                                                keyId, r0, r1))\n"
+                "            return false;\n"
+                "        ct0         = DCRTPolyImpl(c.m_params, Format::EVALUATION, false);\n"
+                "        ct1         = DCRTPolyImpl(c.m_params, Format::EVALUATION, false);\n"
+                "        ct0.pimres_ = r0;\n"
+                "        ct1.pimres_ = r1;\n"
+                "        ct0.pim = ct1.pim = c.pim;\n"
+                "        return true;\n"
+                "    }\n", rel)
     # FHE_B200_ATTACH=1: every DCRTPoly is born attached (pim/PimHook.h default_handle)
     text = once(text, "    std::shared_ptr<PimManager> pim;\n", "    std::shared_ptr<PimManager> pim = pimhook::default_handle();\n", rel)
     text = once(text, "m_vectors{std::move(e.m_vectors)} {}",
@@ -435,4 +461,26 @@ def patch_impl(text):
 
 rewrite("lattice/hal/default/dcrtpoly.h", patch_class)
 rewrite("lattice/hal/default/dcrtpoly-impl.h", patch_impl)
+
+# ---- scheme layer (only the `pke` build uses it): a patched COPY of keyswitch-hybrid.cpp next to the header tree ----
+pke_src = os.path.join(ref, "src", "pke", "lib", "keyswitch", "keyswitch-hybrid.cpp")
+if os.path.exists(pke_src):
+    text = open(pke_src).read()
+    sig = ("                                                                      const EvalKey<DCRTPoly> evalKey) const {\n"
+           "    return EvalFastKeySwitchCore(EvalKeySwitchPrecomputeCore(a, evalKey->GetCryptoParameters()), evalKey,\n")
+    text = once(text, sig,
+                "                                                                      const EvalKey<DCRTPoly> evalKey) const {\n"
+                "    {   // B200 intercept: the whole key switch as one device composition when `a` carries the handle\n"
+                "        const auto cp = std::dynamic_pointer_cast<CryptoParametersRNS>(evalKey->GetCryptoParameters());\n"
+                "        PlaintextModulus t = (cp->GetNoiseScale() == 1) ? 0 : cp->GetPlaintextModulus();\n"
+                "        auto res = std::make_shared<std::vector<DCRTPoly>>(2);\n"
+                "        if (DCRTPoly::PimKeySwitchHybrid(a, evalKey->GetBVector(), evalKey->GetAVector(),\n"
+                "                                         cp->GetParamsP()->GetParams().size(), cp->GetNumPerPartQ(), t, evalKey.get(),\n"
+                "                                         (*res)[0], (*res)[1]))\n"
+                "            return res;\n"
+                "    }\n"
+                "    return EvalFastKeySwitchCore(EvalKeySwitchPrecomputeCore(a, evalKey->GetCryptoParameters()), evalKey,\n",
+                "keyswitch-hybrid.cpp")
+    os.makedirs(os.path.join(out, "_pke_src"), exist_ok=True)
+    open(os.path.join(out, "_pke_src", "keyswitch-hybrid.cpp"), "w").write(text)
 print("hook_patch: patched header tree in", out)

@@ -9,6 +9,7 @@
 // arithmetic.
 #include "openfhe.h"
 
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -191,7 +192,86 @@ static void run_ckks(const char* label, ScalingTechnique st, KeySwitchTechnique 
     std::fprintf(stderr, "%s: %.1f ms, launches so far %ld\n", label, clk.ms(), fhe_launch_count());
 }
 
+// Throughput of the schemes' own operations over `count` independent ciphertexts, the callers' OpenMP loop over
+// ciphertexts outside (the reference's inner loops over towers then run serially, utils/parallel.h): usage
+//   pke-driver-hooked bench <bfv-hps|bfv-behz|bfv-hpspoverq|ckks> <ringDim> <depth> <threads> <count>
+// Prints one JSON line per operation; run with and without FHE_B200_ATTACH=1.
+template <class F>
+static double time_loop(int threads, int count, int reps, F f) {
+    double best = 1e30;
+    for (int r = 0; r < reps; r++) {
+        Clock c;
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 1)
+        for (int i = 0; i < count; i++) f(i);
+        best = std::min(best, c.ms());
+    }
+    return best;
+}
+static int run_bench(const std::string& scheme, uint32_t n, uint32_t depth, int threads, int count) {
+    CryptoContext<DCRTPoly> cc;
+    const bool ckks = scheme == "ckks";
+    if (ckks) {
+        CCParams<CryptoContextCKKSRNS> P;
+        P.SetMultiplicativeDepth(depth);
+        P.SetScalingModSize(50);
+        P.SetScalingTechnique(FIXEDMANUAL);
+        P.SetSecurityLevel(HEStd_NotSet);
+        P.SetRingDim(n);
+        cc = GenCryptoContext(P);
+    } else {
+        CCParams<CryptoContextBFVRNS> P;
+        P.SetPlaintextModulus(65537);
+        P.SetMultiplicativeDepth(depth);
+        P.SetMultiplicationTechnique(scheme == "bfv-behz" ? BEHZ : scheme == "bfv-hpspoverq" ? HPSPOVERQ : HPS);
+        P.SetKeySwitchTechnique(HYBRID);
+        P.SetSecurityLevel(HEStd_NotSet);
+        P.SetRingDim(n);
+        cc = GenCryptoContext(P);
+    }
+    cc->Enable(PKE);
+    cc->Enable(KEYSWITCH);
+    cc->Enable(LEVELEDSHE);
+    auto kp = cc->KeyGen();
+    cc->EvalMultKeyGen(kp.secretKey);
+    cc->EvalRotateKeyGen(kp.secretKey, {1});
+    std::vector<Ciphertext<DCRTPoly>> a(count), b(count), out(count);
+    for (int i = 0; i < count; i++) {
+        Plaintext pa, pb;
+        if (ckks) {
+            pa = cc->MakeCKKSPackedPlaintext(std::vector<double>{0.5 + i, 1.5, 2.5});
+            pb = cc->MakeCKKSPackedPlaintext(std::vector<double>{1.0, 0.25 * i, 3.0});
+        } else {
+            pa = cc->MakePackedPlaintext(std::vector<int64_t>{1 + i, 2, 3});
+            pb = cc->MakePackedPlaintext(std::vector<int64_t>{4, 5 + i, 6});
+        }
+        a[i] = cc->Encrypt(kp.publicKey, pa);
+        b[i] = cc->Encrypt(kp.publicKey, pb);
+    }
+    const size_t towers = a[0]->GetElements()[0].GetNumOfElements();
+    auto report = [&](const char* op, double ms) {
+        std::printf("{\"scheme\": \"%s\", \"op\": \"%s\", \"ring_dim\": %u, \"towers\": %zu, \"threads\": %d, \"count\": %d, \"ms\": %.3f, "
+                    "\"ops_per_s\": %.2f, \"attached\": %s, \"launches\": %ld}\n", scheme.c_str(), op, n, towers, threads, count, ms,
+                    count / (ms * 1e-3), std::getenv("FHE_B200_ATTACH") && std::getenv("FHE_B200_ATTACH")[0] == '1' ? "true" : "false",
+                    fhe_launch_count());
+        std::fflush(stdout);
+    };
+    time_loop(threads, count, 1, [&](int i) { out[i] = cc->EvalMult(a[i], b[i]); });          // warm-up: tables, plans, uploads
+    report("EvalAdd", time_loop(threads, count, 3, [&](int i) { out[i] = cc->EvalAdd(a[i], b[i]); }));
+    report("EvalMult+relin", time_loop(threads, count, 3, [&](int i) { out[i] = cc->EvalMult(a[i], b[i]); }));
+    if (ckks)
+        report("EvalMult+relin+Rescale", time_loop(threads, count, 3, [&](int i) { out[i] = cc->Rescale(cc->EvalMult(a[i], b[i])); }));
+    report("EvalRotate", time_loop(threads, count, 3, [&](int i) { out[i] = cc->EvalRotate(a[i], 1); }));
+    uint64_t h = 0;                                      // read one result back: the digest must not depend on the path
+    for (const auto& e : out[count - 1]->GetElements()) h = digest_poly(e, h);
+    std::fprintf(stderr, "last result digest %016llx\n", (unsigned long long)h);
+    return 0;
+}
+
 int main(int argc, char** argv) {
+    if (argc > 1 && std::string(argv[1]) == "bench") {
+        if (argc < 7) { std::fprintf(stderr, "usage: %s bench <scheme> <ringDim> <depth> <threads> <count>\n", argv[0]); return 2; }
+        return run_bench(argv[2], (uint32_t)std::atoi(argv[3]), (uint32_t)std::atoi(argv[4]), std::atoi(argv[5]), std::atoi(argv[6]));
+    }
     const uint32_t n = argc > 1 ? (uint32_t)std::atoi(argv[1]) : 4096;
     const std::string only = argc > 2 ? argv[2] : "";
     auto want = [&](const char* s) { return only.empty() || only == s; };
