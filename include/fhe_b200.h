@@ -340,6 +340,17 @@ int fhe_deserialize(fhe_ring* ring, fhe_dptr dst, const void* src_host, size_t l
 /* seeded uniform coefficients in [0, q_tower) (synthetic inputs for tests and benchmarks) */
 int fhe_fill_uniform(fhe_ring* ring, fhe_dptr dst, size_t batch, uint64_t seed, int stream);
 
+/* ---- BV key switching: the digit decomposition ---------------------------------------------------- */
+/* DCRTPolyImpl::CRTDecompose(baseBits = 0) (dcrtpoly-impl.h:266-288; KeySwitchBV::EvalKeySwitchPrecomputeCore,
+ * src/pke/lib/keyswitch/keyswitch-bv.cpp:308-312): src over the ring [batch][T][N] in `format` (0 EVALUATION,
+ * 1 COEFFICIENT) -> dst [T][batch][T][N], EVALUATION: digit i holds, in tower k, the COEFFICIENT tower i of src moved to
+ * q_k with NativeVector::SwitchModulus (mubintvecnat.cpp:112-135) and transformed, and in tower i the EVALUATION tower
+ * itself.  The plan holds the T x T switching constants and scratch (one per stream).  src is not modified. */
+typedef struct fhe_crt_decomp fhe_crt_decomp;
+int fhe_crt_decompose_create(fhe_ring* ring, fhe_crt_decomp** out);
+int fhe_crt_decompose_destroy(fhe_crt_decomp* plan);
+int fhe_crt_decompose(fhe_crt_decomp* plan, fhe_dptr dst_digits, fhe_dptr src, size_t batch, int format, int stream);
+
 /* ---- BFV, the BEHZ multiplication technique ------------------------------------------------------- */
 /* ring_qbsk: size_q towers of Q followed by Bsk = B u {msk} (at least one tower of B; msk last), with roots of unity,
  * the ring CryptoParametersBFVRNS builds as m_paramsQBsk (src/pke/lib/scheme/bfvrns/bfvrns-cryptoparameters.cpp:

@@ -199,6 +199,23 @@ private:
   fhe_keyswitch *plan_ = nullptr;
 };
 
+/* DCRTPolyImpl::CRTDecompose(0) over a ring (dcrtpoly-impl.h:266-288): the digits of KeySwitchBV */
+class PimCrtDecomp {
+public:
+  explicit PimCrtDecomp(std::shared_ptr<PimRing> ring) : ring_(std::move(ring)) {
+    PimManager::check(fhe_crt_decompose_create(ring_->handle(), &plan_), "PimCrtDecomp");
+  }
+  ~PimCrtDecomp() { fhe_crt_decompose_destroy(plan_); }
+  PimCrtDecomp(const PimCrtDecomp &) = delete;
+  PimCrtDecomp &operator=(const PimCrtDecomp &) = delete;
+  fhe_crt_decomp *handle() const { return plan_; }
+  const std::shared_ptr<PimRing> &Ring() const { return ring_; }
+
+private:
+  std::shared_ptr<PimRing> ring_;
+  fhe_crt_decomp *plan_ = nullptr;
+};
+
 /* The BEHZ set over a ring Q u Bsk (dcrtpoly-impl.h:2005-2050, 2069-2420; BFV multTech BEHZ): every table of
  * bfvrns-cryptoparameters.cpp:724-891 derived from the moduli and the plaintext modulus t. */
 class PimBehz {

@@ -145,7 +145,8 @@ struct Resident {
   bool device_newer = false;          /* guarded by mu */
   int stream = 0;                     /* the stream whose work wrote `d` last */
   std::mutex mu;
-  ~Resident() { if (d) fhe_free(ctx, d); }
+  std::shared_ptr<void> owner;        /* set: `d` is a view into a block that several device copies share (CRTDecompose) */
+  ~Resident() { if (d && !owner) fhe_free(ctx, d); }
 };
 
 inline long &resident_uploads() { static long n = 0; return n; }     /* counters for the tests */
@@ -998,6 +999,58 @@ inline bool resident_keyswitch_hybrid(PimManager *pim, const Towers &c, std::sha
   finish(ctx);
   r0 = o0;
   r1 = o1;
+  return true;
+}
+
+/* DCRTPolyImpl::CRTDecompose(baseBits = 0) (dcrtpoly-impl.h:266-288; KeySwitchBV's digits): a -> one device copy per
+ * digit, views into one [T][T][N] block (the transform of all digits is one launch sequence) */
+template <class Towers>
+inline bool resident_crt_decompose(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, int format,
+                                   std::vector<std::shared_ptr<Resident>> &digits) {
+  if (!pim || a.empty() || a[0].GetRingDimension() < 2) return false;
+  const int S = hook_stream(pim->context());
+  auto da = ensure_device(pim, a, ra);
+  static std::mutex mu;
+  static std::map<std::pair<PimRing *, int>, CachedPlan<PimCrtDecomp>> cache;
+  CachedPlan<PimCrtDecomp> plan;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto key = std::make_pair(da->ring.get(), S);
+    auto it = cache.find(key);
+    if (it == cache.end()) {
+      CachedPlan<PimCrtDecomp> c;
+      c.plan = std::make_shared<PimCrtDecomp>(da->ring);
+      it = cache.emplace(key, c).first;
+    }
+    plan = it->second;
+  }
+  struct Block {
+    fhe_ctx *ctx;
+    fhe_dptr p = 0;
+    ~Block() { if (p) fhe_free(ctx, p); }
+  };
+  const size_t T = a.size(), n = da->n, poly = T * n * sizeof(uint64_t);
+  auto blk = std::make_shared<Block>();
+  blk->ctx = da->ctx;
+  PimManager::check(fhe_alloc(da->ctx, T * poly, &blk->p), "pim hook: device buffer");
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_crt_decompose(plan.plan->handle(), blk->p, da->d, 1, format, S), "pim hook: CRT decomposition");
+  }
+  finish(da->ctx);
+  digits.clear();
+  for (size_t i = 0; i < T; i++) {
+    auto r = std::make_shared<Resident>();
+    r->ring = da->ring;
+    r->ctx = da->ctx;
+    r->stream = S;
+    r->towers = T;
+    r->n = n;
+    r->d = blk->p + i * poly;
+    r->owner = blk;
+    r->device_newer = true;
+    digits.push_back(r);
+  }
   return true;
 }
 

@@ -1294,3 +1294,33 @@ void orc_behz_scale_and_round(const orc_behz* z, uint64_t* out, const uint64_t* 
     }
     free(p1); free(p2);
 }
+
+/* DCRTPolyImpl::CRTDecompose(baseBits = 0) (dcrtpoly-impl.h:266-288; the digits of KeySwitchBV, keyswitch-bv.cpp:308-312):
+ * in [B][T][N] in `format` (0 EVALUATION, 1 COEFFICIENT) -> out [T][B][T][N], EVALUATION: digit i keeps the stored tower i
+ * and gets, in every other tower k, the COEFFICIENT tower i moved to q_k with NativeVector::SwitchModulus and transformed */
+void orc_crt_decompose(const orc_ctx* c, uint64_t* out, const uint64_t* in, size_t B, int format) {
+    const uint32_t N = c->N, T = c->T;
+    size_t w = B * T * (size_t)N;
+    uint64_t* coef = (uint64_t*)malloc(w * 8);
+    uint64_t* eval = (uint64_t*)malloc(w * 8);
+    memcpy(coef, in, w * 8);
+    memcpy(eval, in, w * 8);
+    if (format == 0) orc_dcrt_ntt(c, 1, coef, B, 0);                     /* :267-270 */
+    else orc_dcrt_ntt(c, 0, eval, B, 0);
+    for (uint32_t i = 0; i < T; i++) {
+        uint64_t* digit = out + (size_t)i * w;
+        for (size_t b = 0; b < B; b++)
+            for (uint32_t k = 0; k < T; k++) {
+                uint64_t* o = digit + (b * T + k) * N;
+                if (k == i) {                                            /* :274 result(size, *eval) */
+                    memcpy(o, eval + (b * T + i) * N, (size_t)N * 8);
+                } else {                                                 /* :280-283 */
+                    const uint64_t* x = coef + (b * T + i) * N;
+                    for (uint32_t n = 0; n < N; n++) o[n] = switch_modulus1(x[n], c->q[i], c->q[k]);
+                    if (!(c->psi[k] == 0 || c->psi[k] == 1))
+                        orc_ntt_fwd(o, N, c->q[k], c->W + (size_t)k * N, c->Wp + (size_t)k * N);
+                }
+            }
+    }
+    free(coef); free(eval);
+}

@@ -102,6 +102,7 @@ void     orc_behz_q_to_bsk_montgomery(const orc_behz* z, uint64_t* out_qbsk, con
 void     orc_behz_fast_rns_floor_q(const orc_behz* z, uint64_t* x_qbsk, size_t B);
 void     orc_behz_fast_base_conv_sk(const orc_behz* z, uint64_t* out_q, const uint64_t* in_qbsk, size_t B);
 void     orc_behz_scale_and_round(const orc_behz* z, uint64_t* out, const uint64_t* in_q, size_t B);
+void     orc_crt_decompose(const orc_ctx* c, uint64_t* out, const uint64_t* in, size_t B, int format);   /* dcrtpoly-impl.h:266-288 */
 int      orc_max_threads(void);
 
 /* ---- automorphism X -> X^k, k odd ----

@@ -411,6 +411,26 @@ def patch_impl(text):
                 "            return dev;\n"
                 "        }\n"
                 "    }\n" + sig, rel)
+    # CRTDecompose(0) (const, returns one polynomial per tower: the digits of KeySwitchBV)
+    sig = ("std::vector<DCRTPolyImpl<VecType>> DCRTPolyImpl<VecType>::CRTDecompose(uint32_t baseBits) const {\n"
+           "    DCRTPolyImpl<VecType> cp(*this);\n")
+    text = once(text, sig,
+                "std::vector<DCRTPolyImpl<VecType>> DCRTPolyImpl<VecType>::CRTDecompose(uint32_t baseBits) const {\n"
+                "    if (pim && baseBits == 0 && !m_vectors_.empty()) {\n"
+                "        std::vector<std::shared_ptr<pimhook::Resident>> dig;\n"
+                "        if (pimhook::resident_crt_decompose(pim.get(), m_vectors_, pimres_, m_format == Format::EVALUATION ? 0 : 1, dig)) {\n"
+                "            std::vector<DCRTPolyType> result;\n"
+                "            result.reserve(dig.size());\n"
+                "            for (auto& r : dig) {\n"
+                "                DCRTPolyImpl<VecType> d(m_params, Format::EVALUATION, false);\n"
+                "                d.pimres_ = r;\n"
+                "                d.pim     = pim;\n"
+                "                result.push_back(std::move(d));\n"
+                "            }\n"
+                "            return result;\n"
+                "        }\n"
+                "    }\n"
+                "    DCRTPolyImpl<VecType> cp(*this);\n", rel)
     # BEHZ: FastBaseConvqToBskMontgomery (in place, Q -> QBsk, EVALUATION), FastRNSFloorq (in place over QBsk),
     # FastBaseConvSK (in place, QBsk -> Q)
     sig = ("    const std::vector<NativeInteger>& mtildeInvModbskPrecon) {\n"

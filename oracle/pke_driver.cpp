@@ -223,7 +223,7 @@ static int run_bench(const std::string& scheme, uint32_t n, uint32_t depth, int 
         P.SetPlaintextModulus(65537);
         P.SetMultiplicativeDepth(depth);
         P.SetMultiplicationTechnique(scheme == "bfv-behz" ? BEHZ : scheme == "bfv-hpspoverq" ? HPSPOVERQ : HPS);
-        P.SetKeySwitchTechnique(HYBRID);
+        P.SetKeySwitchTechnique(scheme == "bfv-bv" ? BV : HYBRID);      // bfv-bv: HPS with the scheme's default key switching
         P.SetSecurityLevel(HEStd_NotSet);
         P.SetRingDim(n);
         cc = GenCryptoContext(P);

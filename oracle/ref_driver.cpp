@@ -1250,4 +1250,34 @@ int ref_polys_behz_scale_and_round(const ref_polys* a, ref_behz* z, uint64_t* ou
     });
 }
 
+// DCRTPoly::CRTDecompose(0) (dcrtpoly-impl.h:266-288): digit `digit` of every polynomial of the batch, as a new batch
+ref_polys* ref_polys_crt_decompose(const ref_polys* a, uint32_t digit) {
+    auto* r = new ref_polys{a->ctx, {}};
+    serial_omp([&] {
+        for (auto& poly : a->v) {
+            auto digits = poly.CRTDecompose(0);
+            r->v.push_back(digits.at(digit));
+        }
+    });
+    return r;
+}
+// KeySwitchBV::EvalFastKeySwitchCore (keyswitch-bv.cpp:314-338) on DCRTPolys of this driver: c over Q (EVALUATION),
+// keys kb / ka = T polynomials over Q each (batch handles of T polys); returns ct0, ct1 (batch of two)
+ref_polys* ref_keyswitch_bv(const ref_polys* c, const ref_polys* kb, const ref_polys* ka) {
+    auto* r = new ref_polys{c->ctx, {}};
+    serial_omp([&] {
+        auto digits = c->v.at(0).CRTDecompose(0);
+        std::vector<DCRTPoly> bv(kb->v), av(ka->v);
+        DCRTPoly ct1 = (av[0] *= digits[0]);
+        DCRTPoly ct0 = (bv[0] *= digits[0]);
+        for (usint i = 1; i < digits.size(); ++i) {
+            ct0 += (bv[i] *= digits[i]);
+            ct1 += (av[i] *= digits[i]);
+        }
+        r->v.push_back(ct0);
+        r->v.push_back(ct1);
+    });
+    return r;
+}
+
 }  // extern "C"

@@ -69,6 +69,7 @@ class Oracle:
             ("orc_behz_fast_rns_floor_q", None, [vp, vp, sz]),
             ("orc_behz_fast_base_conv_sk", None, [vp, vp, vp, sz]),
             ("orc_behz_scale_and_round", None, [vp, vp, vp, sz]),
+            ("orc_crt_decompose", None, [vp, vp, vp, sz, ci]),
             ("orc_keyswitch_digits", u32, [u32, u32]),
             ("orc_keyswitch_precompute", None, [vp, u32, u32, vp, vp, sz]),
             ("orc_keyswitch_inner", None, [vp, u32, vp, vp, vp, vp, vp, sz]),
@@ -208,6 +209,16 @@ class OracleCtx:
         return x
 
 
+def _crt_decompose(self, x, fmt=0):
+    """DCRTPolyImpl::CRTDecompose(0) over [B][T][N] -> [T][B][T][N] (EVALUATION)."""
+    x = np.ascontiguousarray(x, np.uint64)
+    T = len(self.q)
+    batch = x.size // (T * self.n)
+    out = np.empty((T, batch, T, self.n), np.uint64)
+    self.o.L.orc_crt_decompose(self.h, _p(out), _p(x), batch, fmt)
+    return out
+
+
 def _automorphism(self, x, k, fmt=0):
     """DCRTPolyImpl::AutomorphismTransform(k) over [B][T][N]; fmt 0 EVALUATION, 1 COEFFICIENT."""
     x = np.ascontiguousarray(x, np.uint64)
@@ -225,6 +236,7 @@ def _automap(self, n, k):
 
 
 OracleCtx.automorphism = _automorphism
+OracleCtx.crt_decompose = _crt_decompose
 Oracle.automap = _automap
 
 

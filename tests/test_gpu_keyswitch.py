@@ -122,3 +122,33 @@ def test_decrypt_scale_recovers_a_scaled_message(pkg, backend, oracle):
     plan.close()
     backend.free(dx); backend.free(dy)
     ring.close()
+
+
+# ---- BV key switching's digits: DCRTPolyImpl::CRTDecompose(0) (dcrtpoly-impl.h:266-288) ---------------------------
+@pytest.mark.parametrize("logn,nbits,towers,batch,fmt", [
+    (6, 60, 3, 2, 0), (6, 60, 3, 2, 1), (10, 30, 4, 3, 0), (11, 45, 1, 1, 0), (12, 58, 5, 2, 1), (14, 60, 8, 1, 0), (16, 60, 4, 1, 0),
+])
+def test_crt_decompose_vs_oracle(pkg, backend, oracle, logn, nbits, towers, batch, fmt):
+    n = 1 << logn
+    q, psi = oracle.gen_params(nbits, n, towers)
+    if towers >= 4:                                   # a much smaller modulus among large ones: the `v %= nm` path
+        q[1] = oracle.L.orc_next_prime(oracle.L.orc_first_prime(20, 2 * n), 2 * n)
+        psi[1] = oracle.L.orc_root_of_unity(2 * n, int(q[1]))
+    ring = pkg.Ring(backend, n, q, psi)
+    plan = pkg.CrtDecompose(ring)
+    x = oracle.fill_ring(batch, n, q, 611)
+    x[0, :, 0] = q - np.uint64(1)
+    x[0, :, 1] = q >> np.uint64(1)
+    x[0, :, 2] = (q >> np.uint64(1)) + np.uint64(1)
+    dx, dd = backend.alloc(x.nbytes), backend.alloc(towers * x.nbytes)
+    backend.h2d(dx, x)
+    for _ in range(2):
+        plan(dd, dx, batch, fmt)
+        got = backend.d2h(dd, towers * x.size).reshape(towers, batch, towers, n)
+        assert np.array_equal(got, oracle.ctx(n, q, psi).crt_decompose(x, fmt))
+    assert np.array_equal(backend.d2h(dx, x.size).reshape(x.shape), x), "input modified"
+    with pytest.raises(pkg.FheError):
+        plan(dx, dx, batch, fmt)
+    backend.free(dx); backend.free(dd)
+    plan.close()
+    ring.close()

@@ -41,6 +41,10 @@ def load_hooked():
     H.ref_polys_approx_switch.restype = vp
     H.ref_polys_approx_switch.argtypes = [vp, vp]
     H.ref_set_table_tweak.argtypes = [ctypes.c_int]
+    H.ref_polys_crt_decompose.restype = vp
+    H.ref_polys_crt_decompose.argtypes = [vp, u32]
+    H.ref_keyswitch_bv.restype = vp
+    H.ref_keyswitch_bv.argtypes = [vp, vp, vp]
     H.ref_behz_create.restype = vp
     H.ref_behz_create.argtypes = [vp, u32, u64]
     H.ref_behz_destroy.argtypes = [vp]
@@ -316,6 +320,52 @@ def test_resident_behz_evalmult_core(hooked, oracle, pkg, fmt):
         H.ref_polys_free(h)
     H.ref_behz_destroy(z); H.ref_behz_destroy(z2)
     H.ref_ctx_destroy(cQBsk); H.ref_ctx_destroy(cQ)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_resident_crt_decompose_and_bv_key_switch(hooked, oracle, pkg, fmt):
+    """DCRTPolyImpl::CRTDecompose(0) with the handle attached returns device-resident digits (views of one block), and the
+    BV key-switching core built on it (keyswitch-bv.cpp:314-338: sum of digit x key products) stays in HBM."""
+    H = hooked
+    n, T, batch = 1 << 11, 4, 2
+    q, psi = oracle.gen_params(55, n, T)
+    octx = oracle.ctx(n, q, psi)
+    c = H.ref_ctx_create(n, T, p(q), p(psi))
+    x = oracle.fill_ring(batch, n, q, 95)
+    hx = H.ref_polys_load(c, p(x), batch, fmt)
+    assert H.ref_polys_set_pim(hx, 1) == 0, H.ref_last_error()
+    up0, down0 = counters(H)
+    want = octx.crt_decompose(x, fmt)
+    handles = [H.ref_polys_crt_decompose(hx, i) for i in range(T)]
+    assert counters(H) == (up0 + batch, down0)
+    for i, hd in enumerate(handles):
+        got = np.empty((batch, T, n), np.uint64)
+        H.ref_polys_store(hd, p(got))
+        assert np.array_equal(got, want[i]), f"digit {i}"
+        H.ref_polys_free(hd)
+    if fmt == 0:
+        kb, ka = oracle.fill_ring(T, n, q, 96), oracle.fill_ring(T, n, q, 97)
+        x1 = np.ascontiguousarray(x[:1])
+        h1 = H.ref_polys_load(c, p(x1), 1, 0)
+        hb, ha = H.ref_polys_load(c, p(kb), T, 0), H.ref_polys_load(c, p(ka), T, 0)
+        assert H.ref_polys_set_pim(h1, 1) == 0 and H.ref_polys_set_pim(hb, 1) == 0 and H.ref_polys_set_pim(ha, 1) == 0
+        launches0 = pkg._native.lib.fhe_launch_count()
+        hr = H.ref_keyswitch_bv(h1, hb, ha)
+        assert pkg._native.lib.fhe_launch_count() - launches0 >= 2 * T
+        got = np.empty((2, T, n), np.uint64)
+        H.ref_polys_store(hr, p(got))
+        dig = octx.crt_decompose(x1, 0)
+        ct0 = np.zeros((1, T, n), np.uint64)
+        ct1 = np.zeros((1, T, n), np.uint64)
+        for i in range(T):
+            ct0 = octx.elementwise(0, ct0, octx.elementwise(2, kb[i:i + 1], dig[i]))
+            ct1 = octx.elementwise(0, ct1, octx.elementwise(2, ka[i:i + 1], dig[i]))
+        assert np.array_equal(got[0:1], ct0) and np.array_equal(got[1:2], ct1)
+        for h in (h1, hb, ha, hr):
+            H.ref_polys_free(h)
+    H.ref_polys_free(hx)
+    H.ref_ctx_destroy(c)
 
 
 @pytest.mark.gpu

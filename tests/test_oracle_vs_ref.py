@@ -521,3 +521,30 @@ def test_behz_matches_reference(oracle, ref, nbits, nq, nB, t, msk_bits):
     assert np.array_equal(ob.scale_and_round(x), out), "ScaleAndRound(moduliQ, t, tgamma, ...)"
     ref.ref_polys_free(h)
     ref.ref_behz_destroy(z); ref.ref_ctx_destroy(cQBsk); ref.ref_ctx_destroy(cQ)
+
+
+@pytest.mark.parametrize("nbits,n,towers,fmt", [(60, 256, 3, 0), (60, 256, 3, 1), (30, 128, 4, 0), (45, 64, 1, 0), (58, 512, 5, 1)])
+def test_crt_decompose_matches_reference(oracle, ref, nbits, n, towers, fmt):
+    """orc_crt_decompose against DCRTPoly::CRTDecompose(0) (dcrtpoly-impl.h:266-288), every digit, both input formats;
+    moduli of mixed sizes exercise both branches of NativeVector::SwitchModulus."""
+    ref.ref_polys_crt_decompose.restype = vp
+    ref.ref_polys_crt_decompose.argtypes = [vp, u32]
+    q, psi = oracle.gen_params(nbits, n, towers)
+    if towers >= 4:                                   # a much smaller modulus among large ones: the `v %= nm` path
+        q[1] = oracle.L.orc_next_prime(oracle.L.orc_first_prime(20, 2 * n), 2 * n)
+        psi[1] = oracle.L.orc_root_of_unity(2 * n, int(q[1]))
+    B = 2
+    c = ref.ref_ctx_create(n, towers, p(q), p(psi))
+    x = oracle.fill_ring(B, n, q, 511)
+    x[0, :, 0] = q - np.uint64(1)
+    x[0, :, 1] = q >> np.uint64(1)
+    x[0, :, 2] = (q >> np.uint64(1)) + np.uint64(1)
+    hx = ref.ref_polys_load(c, p(x), B, fmt)
+    mine = oracle.ctx(n, q, psi).crt_decompose(x, fmt)
+    for i in range(towers):
+        hd = ref.ref_polys_crt_decompose(hx, i)
+        got = np.empty((B, towers, n), np.uint64)
+        ref.ref_polys_store(hd, p(got))
+        assert np.array_equal(mine[i], got), f"digit {i}"
+        ref.ref_polys_free(hd)
+    ref.ref_polys_free(hx); ref.ref_ctx_destroy(c)

@@ -8,8 +8,8 @@ Importing fails if lib/libfhe_b200.so has not been built: there is no CPU fallba
 """
 from . import _native
 from ._native import FheError, LIB_PATH, OP_ADD, OP_INTT, OP_MUL, OP_NTT, OP_SUB, SIGNATURES
-from .dcrtpoly import (COEFFICIENT, EVALUATION, Backend, Basis, Behz, BfvBehzMult, BfvHpsMult, BfvHpsPOverQMult, Comm, DCRTPolyBatch, DecryptScale, Group, GroupRing, KeySwitch, Rescale, Ring, RingView, ScaleRound, TowerScale,
+from .dcrtpoly import (COEFFICIENT, EVALUATION, Backend, Basis, Behz, CrtDecompose, BfvBehzMult, BfvHpsMult, BfvHpsPOverQMult, Comm, DCRTPolyBatch, DecryptScale, Group, GroupRing, KeySwitch, Rescale, Ring, RingView, ScaleRound, TowerScale,
                        gen_params, hps_p_over_q_tables, hps_scale_tables)
 
-__all__ = ["Backend", "Group", "GroupRing", "Comm", "KeySwitch", "DecryptScale", "Ring", "RingView", "Basis", "Rescale", "ScaleRound", "TowerScale", "Behz", "BfvBehzMult", "BfvHpsMult", "BfvHpsPOverQMult", "hps_scale_tables", "hps_p_over_q_tables", "DCRTPolyBatch", "gen_params", "FheError", "EVALUATION", "COEFFICIENT",
+__all__ = ["Backend", "Group", "GroupRing", "Comm", "KeySwitch", "DecryptScale", "Ring", "RingView", "Basis", "Rescale", "ScaleRound", "TowerScale", "Behz", "CrtDecompose", "BfvBehzMult", "BfvHpsMult", "BfvHpsPOverQMult", "hps_scale_tables", "hps_p_over_q_tables", "DCRTPolyBatch", "gen_params", "FheError", "EVALUATION", "COEFFICIENT",
            "OP_ADD", "OP_SUB", "OP_MUL", "OP_NTT", "OP_INTT", "LIB_PATH", "SIGNATURES"]

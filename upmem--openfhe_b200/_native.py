@@ -98,6 +98,9 @@ SIGNATURES = {
     "fhe_decrypt_scale_destroy": (ci, [vp]),
     "fhe_decrypt_scale_tables": (ci, [vp, vp, vp, vp, vp, ctypes.POINTER(ci)]),
     "fhe_scale_and_round_native": (ci, [vp, u64, u64, sz, ci]),
+    "fhe_crt_decompose_create": (ci, [vp, ctypes.POINTER(vp)]),
+    "fhe_crt_decompose_destroy": (ci, [vp]),
+    "fhe_crt_decompose": (ci, [vp, u64, u64, sz, ci, ci]),
     "fhe_behz_create": (ci, [vp, u32, u64, ctypes.POINTER(vp)]),
     "fhe_behz_destroy": (ci, [vp]),
     "fhe_behz_table": (ci, [vp, ci, vp, ctypes.POINTER(sz)]),

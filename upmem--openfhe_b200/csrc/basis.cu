@@ -541,6 +541,46 @@ cudaError_t launch_rescale_spread(uint64_t* tmp, const uint64_t* last, size_t ba
 }
 
 
+// ---- DCRTPolyImpl::CRTDecompose(0) (dcrtpoly-impl.h:266-288), the digits of KeySwitchBV -------------------------------
+// coef [batch][T][N] (COEFFICIENT) -> out [T][batch][T][N]: digit i, tower k = SwitchModulus(coef tower i, q_i -> q_k), and
+// the tower itself for k = i; the caller then transforms every tower of out (for k = i that restores the stored
+// EVALUATION tower exactly).  sw[i * T + k] = {half = q_i >> 1, q_k, diff, up}.  One thread = one coefficient pair of one
+// source tower, T 16-byte stores: HBM-bound on the writes (8 B read, 8 T B written per coefficient).
+__global__ void __launch_bounds__(256)
+crt_spread_kernel(u64* __restrict__ out, const u64* __restrict__ coef, size_t pairs, u32 logN, u32 T, size_t batch,
+                  const ulonglong4* __restrict__ sw) {
+    const u32 half = logN - 1;
+    for (size_t e = (size_t)blockIdx.x * 256 + threadIdx.x; e < pairs; e += (size_t)gridDim.x * 256) {
+        const size_t unit = e >> half;                         // (batch item, source tower)
+        const u32 i = (u32)(unit % T);
+        const size_t b = unit / T;
+        const u32 n = (u32)((e & ((1u << half) - 1)) << 1);
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(coef + (unit << logN) + n);
+        u64* o = out + ((((size_t)i * batch + b) * T) << logN) + n;
+        for (u32 k = 0; k < T; k++) {
+            ulonglong2 r = v;
+            if (k != i) {
+                const ulonglong4 s = sw[(size_t)i * T + k];
+                r.x = switch_modulus(v.x, s.x, s.y, s.z, s.w != 0);
+                r.y = switch_modulus(v.y, s.x, s.y, s.z, s.w != 0);
+            }
+            *reinterpret_cast<ulonglong2*>(o + ((size_t)k << logN)) = r;
+        }
+    }
+}
+
+cudaError_t launch_crt_spread(uint64_t* out, const uint64_t* coef, size_t batch, uint32_t logN, uint32_t T, const ulonglong4* sw,
+                              cudaStream_t st) {
+    if (batch == 0 || T == 0) return cudaSuccess;
+    if (logN < 1) return cudaErrorInvalidValue;
+    const size_t pairs = (batch * T) << (logN - 1);
+    size_t g = (pairs + 255) / 256;
+    unsigned grid = (unsigned)(g > 148 * 32 ? 148 * 32 : g);
+    crt_spread_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<u64*>(out), reinterpret_cast<const u64*>(coef), pairs, logN, T, batch, sw);
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
+}
+
 // ---- BFV HPSPOVERQ tails ----------------------------------------------------------------------------------------
 // One thread per coefficient pair of one batch item, towers in a loop (every row segment is contiguous in n).
 // k[i] = {c_i, c_i', M_i = q_i * floor(2^63 / q_i), -}.

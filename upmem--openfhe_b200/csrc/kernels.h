@@ -106,6 +106,9 @@ cudaError_t launch_tower_scale(int mode, uint64_t* out, const uint64_t* x, size_
                                uint32_t T, const TowerMod* mods, const ulonglong4* k, cudaStream_t st);
 cudaError_t launch_rescale_spread(uint64_t* tmp, const uint64_t* last, size_t batch, uint32_t logN, uint32_t l, uint64_t ql,
                                   const ulonglong4* sw, const ulonglong4* k, ulonglong2 pre, int bgv, cudaStream_t st);
+// DCRTPolyImpl::CRTDecompose(0): coef [batch][T][N] -> out [T][batch][T][N] in COEFFICIENT form (basis.cu)
+cudaError_t launch_crt_spread(uint64_t* out, const uint64_t* coef, size_t batch, uint32_t logN, uint32_t T, const ulonglong4* sw,
+                              cudaStream_t st);
 // EvalFastKeySwitchCoreExt (keyswitch-hybrid.cpp:442-480): o0 = sum_j digits[j] * kb[j], o1 = sum_j digits[j] * ka[j];
 // digits [np][batch][T][N], keys [np][T][N], outputs [batch][T][N] over the ring r
 cudaError_t launch_ks_inner(const RingDev& r, uint64_t* o0, uint64_t* o1, const uint64_t* digits, const uint64_t* kb,

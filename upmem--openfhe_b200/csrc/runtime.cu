@@ -2087,6 +2087,73 @@ extern "C" int fhe_keyswitch_hybrid(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1
 }
 
 // ---------------------------------------------------------------------------------------------
+// DCRTPolyImpl::CRTDecompose(baseBits = 0) (dcrtpoly-impl.h:266-288): the digits of KeySwitchBV (keyswitch-bv.cpp:308-312)
+// ---------------------------------------------------------------------------------------------
+struct fhe_crt_decomp {
+    fhe_ctx* ctx = nullptr;
+    fhe_ring* ring = nullptr;
+    void* d_sw = nullptr;                         // [T][T] {half = q_i >> 1, q_k, diff, up} (NativeVector::SwitchModulus, q_i -> q_k)
+    Scratch coef;
+};
+
+extern "C" int fhe_crt_decompose_destroy(fhe_crt_decomp* p) {
+    if (!p) return FHE_OK;
+    cudaSetDevice(p->ctx->device);
+    cudaDeviceSynchronize();
+    if (p->d_sw) arena_park(p->ctx, p->d_sw);
+    p->coef.drop(p->ctx);
+    delete p;
+    return FHE_OK;
+}
+
+extern "C" int fhe_crt_decompose_create(fhe_ring* ring, fhe_crt_decomp** out) {
+    if (!ring || !out) return fail(FHE_EINVAL, "fhe_crt_decompose_create: null argument");
+    *out = nullptr;
+    if (ring->dev.N < 2) return fail(FHE_EUNSUPPORTED, "fhe_crt_decompose_create: N must be at least 2");
+    if (!ring->has_ntt && !ring->ntt_identity) return fail(FHE_EINVAL, "fhe_crt_decompose_create: the ring was created without roots of unity");
+    const uint32_t T = ring->dev.T;
+    if (T > 1024) return fail(FHE_EUNSUPPORTED, "fhe_crt_decompose_create: more than 1024 towers");
+    auto* p = new fhe_crt_decomp;
+    p->ctx = ring->ctx; p->ring = ring;
+    std::vector<ulonglong4> sw((size_t)T * T);
+    for (uint32_t i = 0; i < T; i++)
+        for (uint32_t k = 0; k < T; k++) {
+            const uint64_t om = ring->q[i], nm = ring->q[k];
+            const bool up = nm > om;
+            sw[(size_t)i * T + k] = make_ulonglong4(om >> 1, nm, up ? nm - om : nm - (om % nm), up ? 1 : 0);
+        }
+    CUDA_TRY(cudaSetDevice(p->ctx->device));
+    int rc = upload(p->ctx, sw, &p->d_sw);
+    if (rc) { fhe_crt_decompose_destroy(p); return rc; }
+    *out = p;
+    return FHE_OK;
+}
+
+extern "C" int fhe_crt_decompose(fhe_crt_decomp* p, fhe_dptr dst_digits, fhe_dptr src, size_t batch, int format, int stream) {
+    const char* who = "fhe_crt_decompose";
+    if (!p) return fail(FHE_EINVAL, "null CRT decomposition plan");
+    StreamRef s;
+    int rc = ring_stream(p->ring, stream, &s);
+    if (rc) return rc;
+    if (format != 0 && format != 1) return fail(FHE_EINVAL, "%s: format must be 0 (EVALUATION) or 1 (COEFFICIENT)", who);
+    if (batch == 0) return FHE_OK;
+    if (!dst_digits || !src) return fail(FHE_EINVAL, "%s: null device pointer", who);
+    if ((dst_digits | src) & 15) return fail(FHE_EINVAL, "%s: device pointers must be 16-byte aligned", who);
+    if (dst_digits == src) return fail(FHE_EINVAL, "%s: dst must not alias src", who);
+    const uint32_t N = p->ring->dev.N, logN = p->ring->dev.logN, T = p->ring->dev.T;
+    uint64_t* dst = (uint64_t*)(uintptr_t)dst_digits;
+    const uint64_t* in = (const uint64_t*)(uintptr_t)src;
+    const uint64_t* coef = in;
+    if (format == 0) {                                   // :267-270 the COEFFICIENT form, in scratch
+        if ((rc = p->coef.need(p->ctx, batch * T * (size_t)N * 8))) return rc;
+        if ((rc = ring_ntt(p->ring, (uint64_t*)p->coef.p, batch, true, s, who, in, T, T))) return rc;
+        coef = (const uint64_t*)p->coef.p;
+    }
+    CUDA_TRY(launch_crt_spread(dst, coef, batch, logN, T, (const ulonglong4*)p->d_sw, s));      // :276-286
+    return ring_ntt(p->ring, dst, (size_t)T * batch, false, s, who);   // every tower of every digit; tower i of digit i comes back as stored
+}
+
+// ---------------------------------------------------------------------------------------------
 // BEHZ (dcrtpoly-impl.h:2005-2050, 2069-2420): the BFV multiplication technique that the HPS plans above do not cover.
 // A plan over the ring Q u Bsk holds the scheme's tables (bfvrns-cryptoparameters.cpp:662-885, derived from the
 // moduli and t), three conversions built as fhe_basis objects with those tables, and the correction constants of

@@ -761,6 +761,24 @@ class KeySwitch:
         N.check(N.lib.fhe_keyswitch_hybrid(self.h, ct0, ct1, c, evk_b, evk_a, batch, int(t), stream))
 
 
+class CrtDecompose:
+    """DCRTPolyImpl::CRTDecompose(0) (dcrtpoly-impl.h:266-288): src [batch][T][N] -> digits [T][batch][T][N], EVALUATION."""
+
+    def __init__(self, ring):
+        self.ring = ring
+        h = ctypes.c_void_p()
+        N.check(N.lib.fhe_crt_decompose_create(ring.h, ctypes.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            N.lib.fhe_crt_decompose_destroy(self.h)
+            self.h = None
+
+    def __call__(self, dst_digits, src, batch, fmt=EVALUATION, stream=0):
+        N.check(N.lib.fhe_crt_decompose(self.h, dst_digits, src, batch, fmt, stream))
+
+
 class Behz:
     """The BEHZ set of DCRTPolyImpl (dcrtpoly-impl.h:2005-2050, 2069-2420) over `ring_qbsk` = size_q towers of Q followed
     by Bsk = B u {msk}; every table of bfvrns-cryptoparameters.cpp:724-891 is derived on the host from the moduli and t."""
