@@ -922,80 +922,199 @@ struct KeyBlock {          /* evk_b, evk_a as fhe_keyswitch_inner reads them: [d
   }
 };
 
+/* the ring Ql u P of a key switch at the level of `c` (its sizeQl towers), P = the key's last sizeP towers; false when the
+ * key's chain of moduli is not c's */
+template <class Towers>
+inline bool keyswitch_ring(PimManager *pim, const Towers &c, size_t sizeQl, const Towers &key0, size_t sizeP,
+                           std::shared_ptr<PimRing> &ring) {
+  if (key0.size() < sizeQl + sizeP) return false;
+  const size_t sizeQ = key0.size() - sizeP;
+  std::vector<uint64_t> q, psi;
+  for (size_t i = 0; i < sizeQl; i++) {
+    if (key0[i].GetModulus() != c[i].GetModulus()) return false;
+    q.push_back(c[i].GetModulus().ConvertToInt());
+    psi.push_back(c[i].GetRootOfUnity().ConvertToInt());
+  }
+  for (size_t i = sizeQ; i < sizeQ + sizeP; i++) {
+    q.push_back(key0[i].GetModulus().ConvertToInt());
+    psi.push_back(key0[i].GetRootOfUnity().ConvertToInt());
+  }
+  ring = ring_for(pim, (uint32_t)c[0].GetRingDimension(), q, psi);
+  return true;
+}
+
+/* the key's device block for a level: built on the first use (HBM to HBM gathers on stream S), then shared */
+template <class Towers, class KeyAt>
+inline std::shared_ptr<KeyBlock> key_block_for(PimManager *pim, KeyAt key_at, size_t np, size_t sizeQl, size_t sizeP, size_t n,
+                                               const void *key_id, int S) {
+  static std::mutex mu;
+  static std::map<std::tuple<const void *, size_t, fhe_ctx *>, std::shared_ptr<KeyBlock>> keys;
+  static size_t held = 0;
+  fhe_ctx *ctx = pim->context();
+  const size_t T = sizeQl + sizeP;
+  std::lock_guard<std::mutex> lock(mu);
+  KeyRef<Towers> k0 = key_at(0, 0);
+  const size_t sizeQ = k0.towers.size() - sizeP;
+  auto d0 = ensure_device(pim, k0.towers, k0.res);
+  auto id = std::make_tuple(key_id, sizeQl, ctx);
+  auto it = keys.find(id);
+  if (it != keys.end() && it->second->from == d0->d) return it->second;
+  const size_t tower = n * sizeof(uint64_t), bytes = np * T * tower;
+  if (held + 2 * bytes > ((size_t)16 << 30)) { keys.clear(); held = 0; }      /* bounded: blocks in use live on through their shared_ptr */
+  auto kb = std::make_shared<KeyBlock>();
+  kb->ctx = ctx;
+  kb->from = d0->d;
+  kb->bytes = 2 * bytes;
+  PimManager::check(fhe_alloc(ctx, bytes, &kb->b), "pim hook: key block");
+  PimManager::check(fhe_alloc(ctx, bytes, &kb->a), "pim hook: key block");
+  for (int which = 0; which < 2; which++)
+    for (size_t j = 0; j < np; j++) {
+      KeyRef<Towers> kr = key_at(which, j);
+      if (kr.towers.size() != sizeQ + sizeP) return nullptr;
+      auto dk = ensure_device(pim, kr.towers, kr.res);
+      const fhe_dptr dst = (which ? kb->a : kb->b) + j * T * tower;
+      PimManager::check(fhe_d2d(ctx, dst, dk->d, sizeQl * tower, S), "pim hook: key gather");
+      PimManager::check(fhe_d2d(ctx, dst + sizeQl * tower, dk->d + sizeQ * tower, sizeP * tower, S), "pim hook: key gather");
+    }
+  PimManager::check(fhe_sync(ctx, S), "pim hook: key gather");      /* other threads use the block on their own streams */
+  keys[id] = kb;
+  held += 2 * bytes;
+  return kb;
+}
+
+inline std::shared_ptr<Resident> fresh_resident(const std::shared_ptr<PimRing> &ring, fhe_ctx *ctx, int S, size_t towers, size_t n) {
+  auto r = std::make_shared<Resident>();
+  r->ring = ring;
+  r->ctx = ctx;
+  r->stream = S;
+  r->towers = towers;
+  r->n = n;
+  PimManager::check(fhe_alloc(ctx, towers * n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
+  r->device_newer = true;
+  return r;
+}
+
 template <class Towers, class KeyAt>
 inline bool resident_keyswitch_hybrid(PimManager *pim, const Towers &c, std::shared_ptr<Resident> &rc, size_t nkeys, KeyAt key_at,
                                       size_t sizeP, size_t alpha, uint64_t t, const void *key_id, std::shared_ptr<Resident> &r0,
                                       std::shared_ptr<Resident> &r1) {
   if (!pim || c.empty() || sizeP == 0 || alpha == 0 || nkeys == 0) return false;
-  const size_t sizeQl = c.size(), np = (sizeQl + alpha - 1) / alpha, T = sizeQl + sizeP, n = c[0].GetRingDimension();
+  const size_t sizeQl = c.size(), np = (sizeQl + alpha - 1) / alpha, n = c[0].GetRingDimension();
   if (np > nkeys || n < 2) return false;
-  KeyRef<Towers> k0 = key_at(0, 0);
-  if (k0.towers.size() < T) return false;
-  const size_t sizeQ = k0.towers.size() - sizeP;
-  for (size_t i = 0; i < sizeQl; i++)
-    if (k0.towers[i].GetModulus() != c[i].GetModulus()) return false;      /* not the key's own chain of moduli: CPU path */
-  std::vector<uint64_t> q, psi;
-  for (size_t i = 0; i < sizeQl; i++) { q.push_back(c[i].GetModulus().ConvertToInt()); psi.push_back(c[i].GetRootOfUnity().ConvertToInt()); }
-  for (size_t i = sizeQ; i < sizeQ + sizeP; i++) {
-    q.push_back(k0.towers[i].GetModulus().ConvertToInt());
-    psi.push_back(k0.towers[i].GetRootOfUnity().ConvertToInt());
-  }
-  auto ring = ring_for(pim, (uint32_t)n, q, psi);
+  std::shared_ptr<PimRing> ring;
+  if (!keyswitch_ring(pim, c, sizeQl, key_at(0, 0).towers, sizeP, ring)) return false;
   fhe_ctx *ctx = pim->context();
   const int S = hook_stream(ctx);
   auto plan = keyswitch_for(ring, (uint32_t)sizeQl, (uint32_t)alpha);
-  /* the key's device block for this level */
-  static std::mutex mu;
-  static std::map<std::tuple<const void *, size_t, fhe_ctx *>, std::shared_ptr<KeyBlock>> keys;
-  static size_t held = 0;
-  std::shared_ptr<KeyBlock> kb;
-  {
-    std::lock_guard<std::mutex> lock(mu);
-    auto d0 = ensure_device(pim, k0.towers, k0.res);
-    auto id = std::make_tuple(key_id, sizeQl, ctx);
-    auto it = keys.find(id);
-    if (it != keys.end() && it->second->from == d0->d) {
-      kb = it->second;
-    } else {
-      const size_t tower = n * sizeof(uint64_t), bytes = np * T * tower;
-      if (held + 2 * bytes > ((size_t)16 << 30)) { keys.clear(); held = 0; }      /* bounded: blocks in use live on through their shared_ptr */
-      kb = std::make_shared<KeyBlock>();
-      kb->ctx = ctx;
-      kb->from = d0->d;
-      kb->bytes = 2 * bytes;
-      PimManager::check(fhe_alloc(ctx, bytes, &kb->b), "pim hook: key block");
-      PimManager::check(fhe_alloc(ctx, bytes, &kb->a), "pim hook: key block");
-      for (int which = 0; which < 2; which++)
-        for (size_t j = 0; j < np; j++) {
-          KeyRef<Towers> kr = key_at(which, j);
-          if (kr.towers.size() != sizeQ + sizeP) return false;
-          auto dk = ensure_device(pim, kr.towers, kr.res);
-          const fhe_dptr dst = (which ? kb->a : kb->b) + j * T * tower;
-          PimManager::check(fhe_d2d(ctx, dst, dk->d, sizeQl * tower, S), "pim hook: key gather");
-          PimManager::check(fhe_d2d(ctx, dst + sizeQl * tower, dk->d + sizeQ * tower, sizeP * tower, S), "pim hook: key gather");
-        }
-      PimManager::check(fhe_sync(ctx, S), "pim hook: key gather");      /* other threads use the block on their own streams */
-      keys[id] = kb;
-      held += 2 * bytes;
-    }
-  }
+  auto kb = key_block_for<Towers>(pim, key_at, np, sizeQl, sizeP, n, key_id, S);
+  if (!kb) return false;
   auto da = ensure_device(pim, c, rc);
-  auto fresh = [&] {
-    auto r = std::make_shared<Resident>();
-    r->ring = da->ring;
-    r->ctx = ctx;
-    r->stream = S;
-    r->towers = sizeQl;
-    r->n = n;
-    PimManager::check(fhe_alloc(ctx, sizeQl * n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
-    r->device_newer = true;
-    return r;
-  };
-  auto o0 = fresh(), o1 = fresh();
+  auto o0 = fresh_resident(da->ring, ctx, S, sizeQl, n), o1 = fresh_resident(da->ring, ctx, S, sizeQl, n);
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
     PimManager::check(fhe_keyswitch_hybrid(plan.plan->handle(), o0->d, o1->d, da->d, kb->b, kb->a, 1, t, S), "pim hook: hybrid key switch");
   }
+  finish(ctx);
+  r0 = o0;
+  r1 = o1;
+  return true;
+}
+
+struct DeviceBlock {          /* an arena block shared by several device copies (views) */
+  fhe_ctx *ctx;
+  fhe_dptr p = 0;
+  ~DeviceBlock() { if (p) fhe_free(ctx, p); }
+};
+
+/* KeySwitchHYBRID::EvalKeySwitchPrecomputeCore (keyswitch-hybrid.cpp:330-420, the hoisted half of a rotation): c over Ql ->
+ * one device copy per digit over Ql u P, views into one [digits][Ql u P][N] block.  p_q / p_psi = the moduli and roots of P. */
+template <class Towers>
+inline bool resident_keyswitch_digits(PimManager *pim, const Towers &c, std::shared_ptr<Resident> &rc, const std::vector<uint64_t> &p_q,
+                                      const std::vector<uint64_t> &p_psi, size_t alpha, size_t max_digits,
+                                      std::vector<std::shared_ptr<Resident>> &digits) {
+  if (!pim || c.empty() || p_q.empty() || p_q.size() != p_psi.size() || alpha == 0) return false;
+  const size_t sizeQl = c.size(), sizeP = p_q.size(), T = sizeQl + sizeP, n = c[0].GetRingDimension();
+  const size_t np = (sizeQl + alpha - 1) / alpha;
+  if (n < 2 || np > max_digits) return false;
+  std::vector<uint64_t> q, psi;
+  for (size_t i = 0; i < sizeQl; i++) { q.push_back(c[i].GetModulus().ConvertToInt()); psi.push_back(c[i].GetRootOfUnity().ConvertToInt()); }
+  q.insert(q.end(), p_q.begin(), p_q.end());
+  psi.insert(psi.end(), p_psi.begin(), p_psi.end());
+  auto ring = ring_for(pim, (uint32_t)n, q, psi);
+  fhe_ctx *ctx = pim->context();
+  const int S = hook_stream(ctx);
+  auto plan = keyswitch_for(ring, (uint32_t)sizeQl, (uint32_t)alpha);
+  auto da = ensure_device(pim, c, rc);
+  const size_t poly = T * n * sizeof(uint64_t);
+  auto blk = std::make_shared<DeviceBlock>();
+  blk->ctx = ctx;
+  PimManager::check(fhe_alloc(ctx, np * poly, &blk->p), "pim hook: device buffer");
+  {
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_keyswitch_precompute(plan.plan->handle(), blk->p, da->d, 1, S), "pim hook: key-switch digits");
+  }
+  finish(ctx);
+  digits.clear();
+  for (size_t j = 0; j < np; j++) {
+    auto r = std::make_shared<Resident>();
+    r->ring = ring;
+    r->ctx = ctx;
+    r->stream = S;
+    r->towers = T;
+    r->n = n;
+    r->d = blk->p + j * poly;
+    r->owner = blk;
+    r->device_newer = true;
+    digits.push_back(r);
+  }
+  return true;
+}
+
+/* KeySwitchHYBRID::EvalFastKeySwitchCoreExt (keyswitch-hybrid.cpp:442-480): the inner product of the digits with the key,
+ * both halves, over Ql u P.  digit_at(j) = KeyRef of digit j; digits that are consecutive views of one block (what
+ * resident_keyswitch_digits returns) are read in place, others are gathered first. */
+template <class Towers, class DigitAt, class KeyAt>
+inline bool resident_keyswitch_inner(PimManager *pim, size_t np, DigitAt digit_at, size_t nkeys, KeyAt key_at, size_t sizeP, size_t alpha,
+                                     const void *key_id, std::shared_ptr<Resident> &r0, std::shared_ptr<Resident> &r1) {
+  if (!pim || np == 0 || np > nkeys || sizeP == 0 || alpha == 0) return false;
+  KeyRef<Towers> d0 = digit_at(0);
+  const size_t T = d0.towers.size();
+  if (T <= sizeP) return false;
+  const size_t sizeQl = T - sizeP, n = d0.towers[0].GetRingDimension();
+  if (n < 2 || np != (sizeQl + alpha - 1) / alpha) return false;
+  std::shared_ptr<PimRing> ring;
+  if (!keyswitch_ring(pim, d0.towers, sizeQl, key_at(0, 0).towers, sizeP, ring)) return false;
+  {   /* the digits' P towers must be the key's */
+    const Towers &k0 = key_at(0, 0).towers;
+    const size_t sizeQ = k0.size() - sizeP;
+    for (size_t i = 0; i < sizeP; i++)
+      if (d0.towers[sizeQl + i].GetModulus() != k0[sizeQ + i].GetModulus()) return false;
+  }
+  fhe_ctx *ctx = pim->context();
+  const int S = hook_stream(ctx);
+  auto plan = keyswitch_for(ring, (uint32_t)sizeQl, (uint32_t)alpha);
+  auto kb = key_block_for<Towers>(pim, key_at, np, sizeQl, sizeP, n, key_id, S);
+  if (!kb) return false;
+  const size_t poly = T * n * sizeof(uint64_t);
+  std::vector<std::shared_ptr<Resident>> dd;
+  bool contiguous = true;
+  for (size_t j = 0; j < np; j++) {
+    KeyRef<Towers> dj = digit_at(j);
+    if (dj.towers.size() != T) return false;
+    dd.push_back(ensure_device(pim, dj.towers, dj.res));
+    if (dd[j]->d != dd[0]->d + j * poly) contiguous = false;
+  }
+  std::shared_ptr<DeviceBlock> gathered;
+  fhe_dptr base = dd[0]->d;
+  if (!contiguous) {
+    gathered = std::make_shared<DeviceBlock>();
+    gathered->ctx = ctx;
+    PimManager::check(fhe_alloc(ctx, np * poly, &gathered->p), "pim hook: device buffer");
+    for (size_t j = 0; j < np; j++) PimManager::check(fhe_d2d(ctx, gathered->p + j * poly, dd[j]->d, poly, S), "pim hook: digit gather");
+    base = gathered->p;
+  }
+  auto o0 = fresh_resident(ring, ctx, S, T, n), o1 = fresh_resident(ring, ctx, S, T, n);
+  PimManager::check(fhe_keyswitch_inner(plan.plan->handle(), o0->d, o1->d, base, kb->b, kb->a, 1, S), "pim hook: key-switch inner product");
   finish(ctx);
   r0 = o0;
   r1 = o1;

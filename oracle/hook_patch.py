@@ -138,6 +138,54 @@ def patch_class(text):
                 "        ct1.pimres_ = r1;\n"
                 "        ct0.pim = ct1.pim = c.pim;\n"
                 "        return true;\n"
+                "    }\n"
+                "    /* EvalKeySwitchPrecomputeCore (keyswitch-hybrid.cpp:330-420): the digits of c over Ql u P, resident */\n"
+                "    static bool PimKeySwitchDigits(const DCRTPolyImpl& c, const std::shared_ptr<Params>& paramsP,\n"
+                "                                   const std::shared_ptr<Params>& paramsQlP, size_t alpha, size_t maxDigits,\n"
+                "                                   std::vector<DCRTPolyImpl>& out) {\n"
+                "        if (!c.pim || c.m_format != Format::EVALUATION || c.m_vectors_.empty()) return false;\n"
+                "        std::vector<uint64_t> pq, ppsi;\n"
+                "        for (const auto& tp : paramsP->GetParams()) {\n"
+                "            pq.push_back(tp->GetModulus().ConvertToInt());\n"
+                "            ppsi.push_back(tp->GetRootOfUnity().ConvertToInt());\n"
+                "        }\n"
+                "        std::vector<std::shared_ptr<pimhook::Resident>> dig;\n"
+                "        if (!pimhook::resident_keyswitch_digits(c.pim.get(), c.m_vectors_, c.pimres_, pq, ppsi, alpha, maxDigits, dig)) return false;\n"
+                "        out.clear();\n"
+                "        out.reserve(dig.size());\n"
+                "        for (auto& r : dig) {\n"
+                "            DCRTPolyImpl d(paramsQlP, Format::EVALUATION, false);\n"
+                "            d.pimres_ = r;\n"
+                "            d.pim     = c.pim;\n"
+                "            out.push_back(std::move(d));\n"
+                "        }\n"
+                "        return true;\n"
+                "    }\n"
+                "    /* EvalFastKeySwitchCoreExt (keyswitch-hybrid.cpp:442-480): sum_j digits[j] * key[j], both halves, over Ql u P */\n"
+                "    static bool PimKeySwitchInner(const std::vector<DCRTPolyImpl>& digits, const std::vector<DCRTPolyImpl>& bv,\n"
+                "                                  const std::vector<DCRTPolyImpl>& av, size_t sizeP, size_t alpha, const void* keyId,\n"
+                "                                  DCRTPolyImpl& c0, DCRTPolyImpl& c1) {\n"
+                "        if (digits.empty() || !digits[0].pim || bv.empty() || bv.size() != av.size()) return false;\n"
+                "        for (const auto& d : digits)\n"
+                "            if (d.m_format != Format::EVALUATION) return false;\n"
+                "        for (size_t j = 0; j < bv.size(); j++)\n"
+                "            if (bv[j].m_format != Format::EVALUATION || av[j].m_format != Format::EVALUATION) return false;\n"
+                "        using Towers = std::vector<PolyType>;\n"
+                "        auto digitAt = [&](size_t j) { return pimhook::KeyRef<Towers>{digits[j].m_vectors_, digits[j].pimres_}; };\n"
+                "        auto keyAt = [&](int which, size_t j) {\n"
+                "            const DCRTPolyImpl& k = which ? av[j] : bv[j];\n"
+                "            return pimhook::KeyRef<Towers>{k.m_vectors_, k.pimres_};\n"
+                "        };\n"
+                "        std::shared_ptr<pimhook::Resident> r0, r1;\n"
+                "        if (!pimhook::resident_keyswitch_inner<Towers>(digits[0].pim.get(), digits.size(), digitAt, bv.size(), keyAt, sizeP,\n"
+                "                                                       alpha, keyId, r0, r1))\n"
+                "            return false;\n"
+                "        c0         = DCRTPolyImpl(digits[0].m_params, Format::EVALUATION, false);\n"
+                "        c1         = DCRTPolyImpl(digits[0].m_params, Format::EVALUATION, false);\n"
+                "        c0.pimres_ = r0;\n"
+                "        c1.pimres_ = r1;\n"
+                "        c0.pim = c1.pim = digits[0].pim;\n"
+                "        return true;\n"
                 "    }\n", rel)
     # FHE_B200_ATTACH=1: every DCRTPoly is born attached (pim/PimHook.h default_handle)
     text = once(text, "    std::shared_ptr<PimManager> pim;\n", "    std::shared_ptr<PimManager> pim = pimhook::default_handle();\n", rel)
@@ -501,6 +549,30 @@ if os.path.exists(pke_src):
                 "    }\n"
                 "    return EvalFastKeySwitchCore(EvalKeySwitchPrecomputeCore(a, evalKey->GetCryptoParameters()), evalKey,\n",
                 "keyswitch-hybrid.cpp")
+    # the two halves, called separately by the hoisted rotations (EvalFastRotationPrecompute / EvalFastRotation)
+    sig = ("    if (numPartQl > cryptoParams->GetNumberOfQPartitions())\n"
+           "        numPartQl = cryptoParams->GetNumberOfQPartitions();\n\n"
+           "    std::vector<DCRTPoly> partsCt(numPartQl);\n")
+    text = once(text, sig,
+                "    if (numPartQl > cryptoParams->GetNumberOfQPartitions())\n"
+                "        numPartQl = cryptoParams->GetNumberOfQPartitions();\n\n"
+                "    {   // B200 intercept: the digits as one device composition, resident\n"
+                "        std::vector<DCRTPoly> dev;\n"
+                "        if (DCRTPoly::PimKeySwitchDigits(c, paramsP, paramsQlP, alpha, cryptoParams->GetNumberOfQPartitions(), dev))\n"
+                "            return std::make_shared<std::vector<DCRTPoly>>(std::move(dev));\n"
+                "    }\n"
+                "    std::vector<DCRTPoly> partsCt(numPartQl);\n", "keyswitch-hybrid.cpp")
+    sig = ("    size_t sizeQ   = cryptoParams->GetElementParams()->GetParams().size();\n\n"
+           "    DCRTPoly cTilda0(paramsQlP, Format::EVALUATION, true);\n")
+    text = once(text, sig,
+                "    size_t sizeQ   = cryptoParams->GetElementParams()->GetParams().size();\n\n"
+                "    {   // B200 intercept: the inner product with the key on the device copies\n"
+                "        auto res = std::make_shared<std::vector<DCRTPoly>>(2);\n"
+                "        if (DCRTPoly::PimKeySwitchInner(*digits, bv, av, paramsP->GetParams().size(), cryptoParams->GetNumPerPartQ(),\n"
+                "                                        evalKey.get(), (*res)[0], (*res)[1]))\n"
+                "            return res;\n"
+                "    }\n"
+                "    DCRTPoly cTilda0(paramsQlP, Format::EVALUATION, true);\n", "keyswitch-hybrid.cpp")
     os.makedirs(os.path.join(out, "_pke_src"), exist_ok=True)
     open(os.path.join(out, "_pke_src", "keyswitch-hybrid.cpp"), "w").write(text)
 print("hook_patch: patched header tree in", out)

@@ -91,8 +91,15 @@ static void run_bfv(const char* label, MultiplicationTechnique tech, KeySwitchTe
     show(L + ".rot1", crot);
     auto crot2 = cc->EvalRotate(cadd, -2);
     show(L + ".rot-2", crot2);
-    for (auto& item : std::vector<std::pair<std::string, Ciphertext<DCRTPoly>>>{
-             {"add", cadd}, {"sub", csub}, {"mul", cmul}, {"mul2", cmul2}, {"rot1", crot}, {"rot-2", crot2}}) {
+    std::vector<std::pair<std::string, Ciphertext<DCRTPoly>>> results{
+        {"add", cadd}, {"sub", csub}, {"mul", cmul}, {"mul2", cmul2}, {"rot1", crot}, {"rot-2", crot2}};
+    if (tech != HPSPOVERQLEVELED && ks == HYBRID) {     // (the reference's own hoisted rotation throws for HPSPOVERQLEVELED on the CPU path too)
+        auto pre = cc->EvalFastRotationPrecompute(cmul);
+        auto cfr1 = cc->EvalFastRotation(cmul, 1, 2 * ringDim, pre);
+        show(L + ".fastrot1", cfr1);
+        results.push_back({"fastrot1", cfr1});
+    }
+    for (auto& item : results) {
         Plaintext r;
         cc->Decrypt(kp.secretKey, item.second, &r);
         r->SetLength(V1.size());
@@ -182,8 +189,13 @@ static void run_ckks(const char* label, ScalingTechnique st, KeySwitchTechnique 
     show(L + ".rot1", crot);
     auto crot2 = cc->EvalRotate(c1, -2);
     show(L + ".rot-2", crot2);
+    auto pre = cc->EvalFastRotationPrecompute(cmul);                       // hoisted rotations: the digits once, two rotations
+    auto cfr1 = cc->EvalFastRotation(cmul, 1, 2 * ringDim, pre);
+    auto cfr2 = cc->EvalFastRotation(cmul, -2, 2 * ringDim, pre);
+    show(L + ".fastrot1", cfr1);
+    show(L + ".fastrot-2", cfr2);
     for (auto& item : std::vector<std::pair<std::string, Ciphertext<DCRTPoly>>>{
-             {"add", cadd}, {"mul", cmul}, {"mulpt", cpt}, {"square", csq}, {"rot1", crot}, {"rot-2", crot2}}) {
+             {"add", cadd}, {"mul", cmul}, {"mulpt", cpt}, {"square", csq}, {"rot1", crot}, {"rot-2", crot2}, {"fastrot1", cfr1}, {"fastrot-2", cfr2}}) {
         Plaintext r;
         cc->Decrypt(kp.secretKey, item.second, &r);
         r->SetLength(8);
@@ -261,6 +273,13 @@ static int run_bench(const std::string& scheme, uint32_t n, uint32_t depth, int 
     if (ckks)
         report("EvalMult+relin+Rescale", time_loop(threads, count, 3, [&](int i) { out[i] = cc->Rescale(cc->EvalMult(a[i], b[i])); }));
     report("EvalRotate", time_loop(threads, count, 3, [&](int i) { out[i] = cc->EvalRotate(a[i], 1); }));
+    if (scheme != "bfv-bv") {
+        cc->EvalRotateKeyGen(kp.secretKey, {2, 3, 4});
+        report("4 hoisted rotations (EvalFastRotationPrecompute + 4 x EvalFastRotation)", time_loop(threads, count, 3, [&](int i) {
+                   auto pre = cc->EvalFastRotationPrecompute(a[i]);
+                   for (int r = 1; r <= 4; r++) out[i] = cc->EvalFastRotation(a[i], r, 2 * n, pre);
+               }));
+    }
     uint64_t h = 0;                                      // read one result back: the digest must not depend on the path
     for (const auto& e : out[count - 1]->GetElements()) h = digest_poly(e, h);
     std::fprintf(stderr, "last result digest %016llx\n", (unsigned long long)h);
