@@ -19,7 +19,9 @@
 
 #include "PimDCRTPoly.h"
 
+#include <algorithm>
 #include <atomic>
+#include <cstdio>
 #include <cstring>
 #include <cstdlib>
 #include <map>
@@ -209,6 +211,44 @@ inline std::shared_ptr<Resident> ensure_device(PimManager *pim, const Towers &to
   return r;
 }
 
+/* FHE_B200_HOOK_TRACE=1 (debugging aid): which callers force a download.  Counts the return addresses a few frames above
+ * sync_host and prints the most frequent at exit as offsets into their module (resolve with addr2line -f -C -e <module>). */
+#if defined(__GLIBC__)
+#include <dlfcn.h>
+#include <execinfo.h>
+#endif
+inline void download_site() {
+#if defined(__GLIBC__)
+  static const bool on = [] { const char *e = std::getenv("FHE_B200_HOOK_TRACE"); return e && *e && *e != '0'; }();
+  if (!on) return;
+  static std::mutex mu;
+  static std::map<std::vector<void *>, long> hist;
+  static const bool reg = [] {
+    std::atexit([] {
+      std::vector<std::pair<long, std::vector<void *>>> v;
+      for (auto &kv : hist) v.push_back({kv.second, kv.first});
+      std::sort(v.begin(), v.end(), [](const auto &a, const auto &b) { return a.first > b.first; });
+      for (size_t i = 0; i < v.size() && i < 24; i++) {
+        std::fprintf(stderr, "download site %5ld x:", v[i].first);
+        for (void *a : v[i].second) {
+          Dl_info di;
+          if (dladdr(a, &di) && di.dli_fbase) std::fprintf(stderr, " %#lx", (unsigned long)((char *)a - (char *)di.dli_fbase));
+        }
+        std::fprintf(stderr, "\n");
+      }
+    });
+    return true;
+  }();
+  (void)reg;
+  void *bt[8];
+  const int n = backtrace(bt, 8);
+  std::vector<void *> key;
+  for (int i = 2; i < n && i < 6; i++) key.push_back(bt[i]);
+  std::lock_guard<std::mutex> lock(mu);
+  hist[key]++;
+#endif
+}
+
 /* host towers <- device copy if that is newer; every tower is put in `format` (the DCRTPoly's own) */
 template <class Towers, class Format>
 inline void sync_host(Towers &towers, const std::shared_ptr<Resident> &res, Format format) {
@@ -232,6 +272,7 @@ inline void sync_host(Towers &towers, const std::shared_ptr<Resident> &res, Form
   }
   resident_downloads()++;
   res->device_newer = false;
+  download_site();
 }
 
 /* FHE_B200_HOOK_SYNC=1: every hooked operator waits for its kernels (per-operation latency instead of the default
@@ -291,6 +332,8 @@ inline std::shared_ptr<PimManager> default_handle() {
   static std::shared_ptr<PimManager> h = [] {
     const char *e = std::getenv("FHE_B200_ATTACH");
     if (!e || !*e || *e == '0') return std::shared_ptr<PimManager>();
+    if (const char *r = std::getenv("FHE_B200_ATTACH_REPORT"); r && *r && *r != '0')      /* for unmodified programs: proof of use */
+      std::atexit([] { std::fprintf(stderr, "fhe_b200: %ld kernel launches\n", fhe_launch_count()); });
     return std::shared_ptr<PimManager>(PimManager::getPim(16), [](PimManager *) {});      /* 16 streams: see hook_stream */
   }();
   return h;
@@ -399,6 +442,25 @@ inline std::shared_ptr<Resident> new_resident(PimManager *pim, const Towers &tow
   r->n = towers[0].GetRingDimension();
   PimManager::check(fhe_alloc(r->ctx, r->towers * r->n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
   r->device_newer = true;
+  return r;
+}
+
+/* DCRTPolyImpl::DropLastElement(s) (dcrtpoly-impl.h:719-741) on a resident polynomial: towers are contiguous in HBM, so the
+ * polynomial over the first `keep` towers is a prefix of the same block - a view, no kernel, no copy.  `rest` = the host
+ * towers that remain (moduli and roots). */
+template <class Towers>
+inline std::shared_ptr<Resident> resident_prefix(PimManager *pim, const std::shared_ptr<Resident> &full, const Towers &rest) {
+  if (!full || rest.empty() || rest.size() > full->towers) return nullptr;
+  auto r = std::make_shared<Resident>();
+  std::lock_guard<std::mutex> lock(full->mu);
+  r->ring = ring_of(pim, rest);
+  r->ctx = full->ctx;
+  r->stream = full->stream;
+  r->towers = rest.size();
+  r->n = full->n;
+  r->d = full->d;
+  r->owner = full;                  /* keeps the block alive; the view itself frees nothing */
+  r->device_newer = full->device_newer;
   return r;
 }
 

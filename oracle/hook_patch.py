@@ -76,6 +76,12 @@ ACCESSORS = """
     }
     mutable std::vector<PolyType> m_vectors_;
     mutable std::shared_ptr<pimhook::Resident> pimres_;
+
+public:
+    /* the tower count needs no host values: GetNumOfElements() must not force a download */
+    size_t PimNumTowers() const { return m_vectors_.size(); }
+
+protected:
 """
 HOOK_EQ = ("\n    if (pim && pimhook::resident_eq(pim.get(), m_vectors_, pimres_, rhs.m_vectors_, rhs.pimres_, %s))"
            "\n        return *this;")
@@ -459,6 +465,50 @@ def patch_impl(text):
                 "            return dev;\n"
                 "        }\n"
                 "    }\n" + sig, rel)
+    # Times(std::vector<Integer>) (dcrtpoly-impl.h:608-615: CKKS scaling-factor adjustments): the per-tower constants as
+    # NativeIntegers, then the same device path as Times(std::vector<NativeInteger>)
+    sig = ("DCRTPolyImpl<VecType> DCRTPolyImpl<VecType>::Times(const std::vector<Integer>& crtElement) const {\n"
+           "    DCRTPolyImpl<VecType> tmp(m_params, m_format);\n")
+    text = once(text, sig,
+                "DCRTPolyImpl<VecType> DCRTPolyImpl<VecType>::Times(const std::vector<Integer>& crtElement) const {\n"
+                "    if (pim && !m_vectors_.empty() && crtElement.size() >= m_vectors_.size()) {\n"
+                "        std::vector<NativeInteger> nat(m_vectors_.size());\n"
+                "        for (size_t i = 0; i < nat.size(); ++i) nat[i] = NativeInteger(crtElement[i]);\n"
+                "        DCRTPolyImpl<VecType> dev(m_params, m_format, false);\n"
+                "        if (pimhook::resident_tower_scale(pim.get(), 2, m_vectors_, pimres_, dev.m_vectors_, dev.pimres_, nat)) {\n"
+                "            dev.pim = pim;\n"
+                "            return dev;\n"
+                "        }\n"
+                "    }\n"
+                "    DCRTPolyImpl<VecType> tmp(m_params, m_format);\n", rel)
+    # DropLastElement / DropLastElements on a resident polynomial: the device copy shrinks to a prefix view, nothing moves
+    sig = ("        OPENFHE_THROW(config_error, \"Removing last element of DCRTPoly object renders it invalid!\");\n"
+           "    m_vectors.resize(m_vectors.size() - 1);\n")
+    text = once(text, sig,
+                "        OPENFHE_THROW(config_error, \"Removing last element of DCRTPoly object renders it invalid!\");\n"
+                "    if (pim && pimres_) {\n"
+                "        m_vectors_.resize(m_vectors_.size() - 1);\n"
+                "        DCRTPolyImpl::Params* shorter = new DCRTPolyImpl::Params(*m_params);\n"
+                "        shorter->PopLastParam();\n"
+                "        m_params.reset(shorter);\n"
+                "        pimres_ = pimhook::resident_prefix(pim.get(), pimres_, m_vectors_);\n"
+                "        return;\n"
+                "    }\n"
+                "    m_vectors.resize(m_vectors.size() - 1);\n", rel)
+    sig = ("                      \"perform the modulus reduction\");\n    }\n"
+           "    m_vectors.resize(m_vectors.size() - i);\n")
+    text = once(text, sig,
+                "                      \"perform the modulus reduction\");\n    }\n"
+                "    if (pim && pimres_) {\n"
+                "        m_vectors_.resize(m_vectors_.size() - i);\n"
+                "        DCRTPolyImpl::Params* shorter = new DCRTPolyImpl::Params(*m_params);\n"
+                "        for (size_t j = 0; j < i; j++)\n"
+                "            shorter->PopLastParam();\n"
+                "        m_params.reset(shorter);\n"
+                "        pimres_ = pimhook::resident_prefix(pim.get(), pimres_, m_vectors_);\n"
+                "        return;\n"
+                "    }\n"
+                "    m_vectors.resize(m_vectors.size() - i);\n", rel)
     # CRTDecompose(0) (const, returns one polynomial per tower: the digits of KeySwitchBV)
     sig = ("std::vector<DCRTPolyImpl<VecType>> DCRTPolyImpl<VecType>::CRTDecompose(uint32_t baseBits) const {\n"
            "    DCRTPolyImpl<VecType> cp(*this);\n")
@@ -527,6 +577,12 @@ def patch_impl(text):
     return head + "#define m_vectors PimHostVectors()\n" + sep + tail + "\n#undef m_vectors\n"
 
 
+def patch_interface(text):
+    return once(text, "        return this->GetDerived().GetAllElements().size();\n",
+                "        return this->GetDerived().PimNumTowers();\n", "dcrtpoly-interface.h")
+
+
+rewrite("lattice/hal/dcrtpoly-interface.h", patch_interface)
 rewrite("lattice/hal/default/dcrtpoly.h", patch_class)
 rewrite("lattice/hal/default/dcrtpoly-impl.h", patch_impl)
 

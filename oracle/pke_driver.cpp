@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "fhe_b200.h"
+#include <omp.h>
 
 using namespace lbcrypto;
 
@@ -286,7 +287,66 @@ static int run_bench(const std::string& scheme, uint32_t n, uint32_t depth, int 
     return 0;
 }
 
+// CKKS bootstrapping with the parameters of the reference's src/pke/examples/simple-ckks-bootstrapping.cpp at a chosen ring
+// dimension and slot count: times EvalBootstrap alone.  usage: pke-driver-hooked bootstrap <ringDim> <slots> <reps>
+static int run_bootstrap(uint32_t n, uint32_t slots, int reps) {
+    CCParams<CryptoContextCKKSRNS> P;
+    SecretKeyDist skd = UNIFORM_TERNARY;
+    P.SetSecretKeyDist(skd);
+    P.SetSecurityLevel(HEStd_NotSet);
+    P.SetRingDim(n);
+    P.SetScalingModSize(59);
+    P.SetScalingTechnique(FLEXIBLEAUTO);
+    P.SetFirstModSize(60);
+    std::vector<uint32_t> levelBudget = {4, 4};
+    usint depth = 10 + FHECKKSRNS::GetBootstrapDepth(levelBudget, skd);
+    P.SetMultiplicativeDepth(depth);
+    CryptoContext<DCRTPoly> cc = GenCryptoContext(P);
+    cc->Enable(PKE);
+    cc->Enable(KEYSWITCH);
+    cc->Enable(LEVELEDSHE);
+    cc->Enable(ADVANCEDSHE);
+    cc->Enable(FHE);
+    Clock setup;
+    cc->EvalBootstrapSetup(levelBudget, {0, 0}, slots);
+    auto kp = cc->KeyGen();
+    cc->EvalMultKeyGen(kp.secretKey);
+    cc->EvalBootstrapKeyGen(kp.secretKey, slots);
+    const double setup_ms = setup.ms();
+    std::vector<double> x = {0.25, 0.5, 0.75, 1.0, 2.0, 3.0, 4.0, 5.0};
+    Plaintext pt = cc->MakeCKKSPackedPlaintext(x, 1, depth - 1, nullptr, slots);
+    pt->SetLength(x.size());
+    auto ct = cc->Encrypt(kp.publicKey, pt);
+    Ciphertext<DCRTPoly> after;
+    double best = 1e30;
+    for (int r = 0; r < reps; r++) {
+        const long up0 = pimhook::resident_uploads(), down0 = pimhook::resident_downloads(), l0 = fhe_launch_count();
+        Clock c;
+        after = cc->EvalBootstrap(ct);
+        std::fprintf(stderr, "bootstrap rep %d: %ld polynomials uploaded, %ld downloaded, %ld launches\n", r,
+                     pimhook::resident_uploads() - up0, pimhook::resident_downloads() - down0, fhe_launch_count() - l0);
+        uint64_t h = 0;                                  // reading the result ends the measurement (the device work is asynchronous)
+        for (const auto& e : after->GetElements()) h = digest_poly(e, h);
+        best = std::min(best, c.ms());
+        std::fprintf(stderr, "bootstrap rep %d: digest %016llx\n", r, (unsigned long long)h);
+    }
+    Plaintext res;
+    cc->Decrypt(kp.secretKey, after, &res);
+    res->SetLength(x.size());
+    show("bootstrap.dec", res->GetRealPackedValue());
+    const char* att = std::getenv("FHE_B200_ATTACH");
+    std::printf("{\"scheme\": \"ckks\", \"op\": \"EvalBootstrap\", \"ring_dim\": %u, \"slots\": %u, \"towers\": %zu, \"threads\": %d, \"ms\": %.1f, "
+                "\"setup_keygen_ms\": %.0f, \"levels_after\": %u, \"attached\": %s, \"launches\": %ld}\n", n, slots,
+                (size_t)cc->GetCryptoParameters()->GetElementParams()->GetParams().size(), omp_get_max_threads(), best, setup_ms,
+                (unsigned)(depth - after->GetLevel()), att && att[0] == '1' ? "true" : "false", fhe_launch_count());
+    return 0;
+}
+
 int main(int argc, char** argv) {
+    if (argc > 1 && std::string(argv[1]) == "bootstrap") {
+        if (argc < 5) { std::fprintf(stderr, "usage: %s bootstrap <ringDim> <slots> <reps>\n", argv[0]); return 2; }
+        return run_bootstrap((uint32_t)std::atoi(argv[2]), (uint32_t)std::atoi(argv[3]), std::atoi(argv[4]));
+    }
     if (argc > 1 && std::string(argv[1]) == "bench") {
         if (argc < 7) { std::fprintf(stderr, "usage: %s bench <scheme> <ringDim> <depth> <threads> <count>\n", argv[0]); return 2; }
         return run_bench(argv[2], (uint32_t)std::atoi(argv[3]), (uint32_t)std::atoi(argv[4]), std::atoi(argv[5]), std::atoi(argv[6]));

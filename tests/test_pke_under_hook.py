@@ -42,3 +42,24 @@ def test_schemes_on_the_gpu_equal_the_cpu_path(ring_dim):
     assert len(cpu) == len(gpu) > 90
     for a, b in zip(cpu, gpu):
         assert a == b, f"CPU path: {a}\nGPU path: {b}\n{err[-1500:]}"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("example", ["simple-ckks-bootstrapping", "simple-integers"])
+def test_reference_examples_unmodified(example):
+    """The reference's own src/pke/examples/<example>.cpp, source untouched (`make -C oracle example-<example>`), with
+    every DCRTPoly on the GPU (FHE_B200_ATTACH=1) prints exactly what it prints on the CPU path — CKKS bootstrapping
+    included (linear transforms with hoisted rotations, Chebyshev evaluation, rescaling, level reduction)."""
+    binary = os.path.join(ROOT, "oracle", "_ref", "example-" + example)
+    if not os.path.exists(binary):
+        pytest.skip("example binary not built here")
+    outs = []
+    for attach in ("0", "1"):
+        env = dict(os.environ, OMP_NUM_THREADS="1", FHE_B200_ATTACH=attach, FHE_B200_ATTACH_REPORT="1")
+        r = subprocess.run([binary], env=env, capture_output=True, text=True, timeout=900)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(r)
+    assert outs[0].stdout == outs[1].stdout and len(outs[0].stdout) > 50
+    m = re.search(r"fhe_b200: (\d+) kernel launches", outs[1].stderr)
+    assert m and int(m.group(1)) > 20, outs[1].stderr[-500:]
+    assert "kernel launches" not in outs[0].stderr
