@@ -147,6 +147,11 @@ int fhe_ring_table(const fhe_ring* ring, uint32_t tower, int which, uint64_t* ou
 /* ---- the hot path: device-resident operands -------------------------------------------------- */
 /* dst = a (op) b for every tower of every polynomial of the batch; dst may alias a or b. */
 int fhe_dcrt_op(fhe_ring* ring, int op, fhe_dptr dst, fhe_dptr a, fhe_dptr b, size_t batch, int stream);
+/* dst = a (+|-) scalars[tower] for every coefficient of every tower (op FHE_OP_ADD / FHE_OP_SUB; one host constant per tower,
+ * reduced modulo q_tower first as NativeVector::ModAdd / ModSub do): DCRTPolyImpl::Plus / Minus(const std::vector<Integer>&)
+ * (dcrtpoly-impl.h:556-563, 577-584; Plus in EVALUATION format - in COEFFICIENT format the reference adds to coefficient 0
+ * only, which this call does not do).  dst may be a.  At most 64 towers. */
+int fhe_dcrt_op_scalars(fhe_ring* ring, int op, fhe_dptr dst, fhe_dptr a, const uint64_t* scalars, size_t batch, int stream);
 /* in-place COEFFICIENT -> EVALUATION (bit-reversed order), and back */
 int fhe_ntt_forward(fhe_ring* ring, fhe_dptr x, size_t batch, int stream);
 int fhe_ntt_inverse(fhe_ring* ring, fhe_dptr x, size_t batch, int stream);

@@ -178,6 +178,8 @@ inline void join_stream(const std::shared_ptr<Resident> &r, int S) {
   if (r && r->stream != S) PimManager::check(fhe_sync(r->ctx, r->stream), "pim hook: stream hand-over");
 }
 
+inline void trace_site(int kind);
+
 /* makes `towers` resident (uploading them if they are not yet) and returns the device copy */
 template <class Towers>
 inline std::shared_ptr<Resident> ensure_device(PimManager *pim, const Towers &towers, std::shared_ptr<Resident> &res) {
@@ -207,6 +209,7 @@ inline std::shared_ptr<Resident> ensure_device(PimManager *pim, const Towers &to
     PimManager::check(fhe_sync(r->ctx, S), "pim hook: sync");   /* the staging block is reused after this */
   }
   resident_uploads()++;
+  trace_site(1);
   std::atomic_store(&res, r);
   return r;
 }
@@ -217,24 +220,26 @@ inline std::shared_ptr<Resident> ensure_device(PimManager *pim, const Towers &to
 #include <dlfcn.h>
 #include <execinfo.h>
 #endif
-inline void download_site() {
+inline void trace_site(int kind) {      /* kind 0: download, 1: upload */
 #if defined(__GLIBC__)
   static const bool on = [] { const char *e = std::getenv("FHE_B200_HOOK_TRACE"); return e && *e && *e != '0'; }();
   if (!on) return;
   static std::mutex mu;
-  static std::map<std::vector<void *>, long> hist;
+  static std::map<std::vector<void *>, long> hist[2];
   static const bool reg = [] {
     std::atexit([] {
-      std::vector<std::pair<long, std::vector<void *>>> v;
-      for (auto &kv : hist) v.push_back({kv.second, kv.first});
-      std::sort(v.begin(), v.end(), [](const auto &a, const auto &b) { return a.first > b.first; });
-      for (size_t i = 0; i < v.size() && i < 24; i++) {
-        std::fprintf(stderr, "download site %5ld x:", v[i].first);
-        for (void *a : v[i].second) {
-          Dl_info di;
-          if (dladdr(a, &di) && di.dli_fbase) std::fprintf(stderr, " %#lx", (unsigned long)((char *)a - (char *)di.dli_fbase));
+      for (int k = 0; k < 2; k++) {
+        std::vector<std::pair<long, std::vector<void *>>> v;
+        for (auto &kv : hist[k]) v.push_back({kv.second, kv.first});
+        std::sort(v.begin(), v.end(), [](const auto &a, const auto &b) { return a.first > b.first; });
+        for (size_t i = 0; i < v.size() && i < 16; i++) {
+          std::fprintf(stderr, "%s site %5ld x:", k ? "upload" : "download", v[i].first);
+          for (void *a : v[i].second) {
+            Dl_info di;
+            if (dladdr(a, &di) && di.dli_fbase) std::fprintf(stderr, " %#lx", (unsigned long)((char *)a - (char *)di.dli_fbase));
+          }
+          std::fprintf(stderr, "\n");
         }
-        std::fprintf(stderr, "\n");
       }
     });
     return true;
@@ -245,7 +250,7 @@ inline void download_site() {
   std::vector<void *> key;
   for (int i = 2; i < n && i < 6; i++) key.push_back(bt[i]);
   std::lock_guard<std::mutex> lock(mu);
-  hist[key]++;
+  hist[kind][key]++;
 #endif
 }
 
@@ -272,7 +277,7 @@ inline void sync_host(Towers &towers, const std::shared_ptr<Resident> &res, Form
   }
   resident_downloads()++;
   res->device_newer = false;
-  download_site();
+  trace_site(0);
 }
 
 /* FHE_B200_HOOK_SYNC=1: every hooked operator waits for its kernels (per-operation latency instead of the default
@@ -462,6 +467,23 @@ inline std::shared_ptr<Resident> resident_prefix(PimManager *pim, const std::sha
   r->owner = full;                  /* keeps the block alive; the view itself frees nothing */
   r->device_newer = full->device_newer;
   return r;
+}
+
+/* DCRTPolyImpl::Plus / Minus(const std::vector<Integer>&) (dcrtpoly-impl.h:556-563, 577-584): out = a (+|-) one constant per
+ * tower, every coefficient.  (Plus: EVALUATION format only - the caller checks.) */
+template <class Towers, class IntVec>
+inline bool resident_tower_scalars(PimManager *pim, int op, const Towers &a, std::shared_ptr<Resident> &ra, const Towers &out,
+                                   std::shared_ptr<Resident> &rout, const IntVec &c) {
+  if (!pim || a.empty() || a.size() > 64 || out.size() != a.size() || c.size() < a.size() || a[0].GetRingDimension() < 2) return false;
+  const int S = hook_stream(pim->context());
+  auto da = ensure_device(pim, a, ra);
+  auto r = new_resident(pim, out);
+  uint64_t k[64];
+  for (size_t i = 0; i < a.size(); i++) k[i] = c[i].ConvertToInt();
+  PimManager::check(fhe_dcrt_op_scalars(da->ring->handle(), op, r->d, da->d, k, 1, S), "pim hook: tower scalars");
+  finish(r->ctx);
+  rout = r;
+  return true;
 }
 
 /* DCRTPolyImpl::AutomorphismTransform (dcrtpoly-impl.h:348-369): out = sigma_k(a); format 0 EVALUATION, 1 COEFFICIENT */

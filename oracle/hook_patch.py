@@ -53,13 +53,19 @@ ACCESSORS = """
     /* B200 intercept, resident form (pim/PimHook.h): host view of the towers.  const: refresh from the device copy
      * if that is newer.  non-const: refresh, then drop the device copy (the caller may write). */
     const std::vector<PolyType>& PimHostVectors() const {
-        if (pimres_) pimhook::sync_host(m_vectors_, pimres_, m_format);       /* one predictable branch: the reference reads m_vectors[i][j] in inner loops */
+        if (pimres_) {       /* one predictable branch: the reference reads m_vectors[i][j] in inner loops */
+            auto r = std::atomic_load(&pimres_);      /* may be entered from the threads of an OpenMP loop over towers at once */
+            if (r) pimhook::sync_host(m_vectors_, r, m_format);
+        }
         return m_vectors_;
     }
     std::vector<PolyType>& PimHostVectors() {
         if (pimres_) {
-            pimhook::sync_host(m_vectors_, pimres_, m_format);
-            pimres_.reset();
+            auto r = std::atomic_load(&pimres_);
+            if (r) {
+                pimhook::sync_host(m_vectors_, r, m_format);      /* serialised by the copy's own mutex; the second thread finds it done */
+                std::atomic_store(&pimres_, std::shared_ptr<pimhook::Resident>());
+            }
         }
         return m_vectors_;
     }
@@ -145,6 +151,19 @@ def patch_class(text):
                 "        ct0.pim = ct1.pim = c.pim;\n"
                 "        return true;\n"
                 "    }\n"
+                "    /* KeySwitchExt / EvalFastRotationExt (keyswitch-hybrid.cpp:231-256, ckksrns-leveledshe.cpp:402-460): c over Ql times\n"
+                "     * per-tower constants, extended by zero towers to paramsExt (Ql u P) - instead of TimesNoCheck + SetElementAtIndex */\n"
+                "    static bool PimExtendTimes(const DCRTPolyImpl& c, const std::vector<NativeInteger>& consts,\n"
+                "                               const std::shared_ptr<Params>& paramsExt, DCRTPolyImpl& out) {\n"
+                "        if (!c.pim || c.m_format != Format::EVALUATION || c.m_vectors_.empty() || consts.size() < c.m_vectors_.size() ||\n"
+                "            paramsExt->GetParams().size() <= c.m_vectors_.size())\n"
+                "            return false;\n"
+                "        DCRTPolyImpl dev(paramsExt, Format::EVALUATION, false);\n"
+                "        if (!pimhook::resident_tower_scale(c.pim.get(), 0, c.m_vectors_, c.pimres_, dev.m_vectors_, dev.pimres_, consts)) return false;\n"
+                "        dev.pim = c.pim;\n"
+                "        out     = std::move(dev);\n"
+                "        return true;\n"
+                "    }\n"
                 "    /* EvalKeySwitchPrecomputeCore (keyswitch-hybrid.cpp:330-420): the digits of c over Ql u P, resident */\n"
                 "    static bool PimKeySwitchDigits(const DCRTPolyImpl& c, const std::shared_ptr<Params>& paramsP,\n"
                 "                                   const std::shared_ptr<Params>& paramsQlP, size_t alpha, size_t maxDigits,\n"
@@ -212,6 +231,8 @@ def patch_class(text):
         checks = text[start:at].replace("m_vectors", "m_vectors_")
         text = text[:start] + checks + HOOK_BIN % opc + text[at:]
     # everything else in this header reads the towers through the accessor
+    # the tower COUNT needs no host values (and must not drop the device copy): read it from the member directly
+    text = text.replace("m_vectors.size()", "m_vectors_.size()")
     head, sep, tail = text.partition("namespace lbcrypto {")
     return head + "#define m_vectors PimHostVectors()\n" + sep + tail + "\n#undef m_vectors\n"
 
@@ -481,17 +502,33 @@ def patch_impl(text):
                 "        }\n"
                 "    }\n"
                 "    DCRTPolyImpl<VecType> tmp(m_params, m_format);\n", rel)
+    # Plus / Minus(std::vector<Integer>) (dcrtpoly-impl.h:556-563, 577-584: CKKS EvalAdd / EvalSub with a real constant)
+    for name, opc, cond in (("Plus", "FHE_OP_ADD", " && m_format == Format::EVALUATION"), ("Minus", "FHE_OP_SUB", "")):
+        sig = ("DCRTPolyImpl<VecType> DCRTPolyImpl<VecType>::%s(const std::vector<Integer>& crtElement) const {\n"
+               "    DCRTPolyImpl<VecType> tmp(m_params, m_format);\n" % name)
+        text = once(text, sig,
+                    "DCRTPolyImpl<VecType> DCRTPolyImpl<VecType>::%s(const std::vector<Integer>& crtElement) const {\n"
+                    "    if (pim && !m_vectors_.empty() && crtElement.size() >= m_vectors_.size()%s) {\n"
+                    "        std::vector<NativeInteger> nat(m_vectors_.size());\n"
+                    "        for (size_t i = 0; i < nat.size(); ++i) nat[i] = NativeInteger(crtElement[i]);\n"
+                    "        DCRTPolyImpl<VecType> dev(m_params, m_format, false);\n"
+                    "        if (pimhook::resident_tower_scalars(pim.get(), %s, m_vectors_, pimres_, dev.m_vectors_, dev.pimres_, nat)) {\n"
+                    "            dev.pim = pim;\n"
+                    "            return dev;\n"
+                    "        }\n"
+                    "    }\n"
+                    "    DCRTPolyImpl<VecType> tmp(m_params, m_format);\n" % (name, cond, opc), rel)
     # DropLastElement / DropLastElements on a resident polynomial: the device copy shrinks to a prefix view, nothing moves
     sig = ("        OPENFHE_THROW(config_error, \"Removing last element of DCRTPoly object renders it invalid!\");\n"
            "    m_vectors.resize(m_vectors.size() - 1);\n")
     text = once(text, sig,
                 "        OPENFHE_THROW(config_error, \"Removing last element of DCRTPoly object renders it invalid!\");\n"
-                "    if (pim && pimres_) {\n"
+                "    if (pimres_) {\n"
                 "        m_vectors_.resize(m_vectors_.size() - 1);\n"
                 "        DCRTPolyImpl::Params* shorter = new DCRTPolyImpl::Params(*m_params);\n"
                 "        shorter->PopLastParam();\n"
                 "        m_params.reset(shorter);\n"
-                "        pimres_ = pimhook::resident_prefix(pim.get(), pimres_, m_vectors_);\n"
+                "        pimres_ = pimhook::resident_prefix(pimres_->ring->manager(), pimres_, m_vectors_);\n"
                 "        return;\n"
                 "    }\n"
                 "    m_vectors.resize(m_vectors.size() - 1);\n", rel)
@@ -499,13 +536,13 @@ def patch_impl(text):
            "    m_vectors.resize(m_vectors.size() - i);\n")
     text = once(text, sig,
                 "                      \"perform the modulus reduction\");\n    }\n"
-                "    if (pim && pimres_) {\n"
+                "    if (pimres_) {\n"
                 "        m_vectors_.resize(m_vectors_.size() - i);\n"
                 "        DCRTPolyImpl::Params* shorter = new DCRTPolyImpl::Params(*m_params);\n"
                 "        for (size_t j = 0; j < i; j++)\n"
                 "            shorter->PopLastParam();\n"
                 "        m_params.reset(shorter);\n"
-                "        pimres_ = pimhook::resident_prefix(pim.get(), pimres_, m_vectors_);\n"
+                "        pimres_ = pimhook::resident_prefix(pimres_->ring->manager(), pimres_, m_vectors_);\n"
                 "        return;\n"
                 "    }\n"
                 "    m_vectors.resize(m_vectors.size() - i);\n", rel)
@@ -573,6 +610,8 @@ def patch_impl(text):
                 "        }\n"
                 "    }\n"
                 "    // Input: poly in basis Bsk\n", rel)
+    # the tower COUNT needs no host values (and must not drop the device copy): read it from the member directly
+    text = text.replace("m_vectors.size()", "m_vectors_.size()")
     head, sep, tail = text.partition("namespace lbcrypto {")
     return head + "#define m_vectors PimHostVectors()\n" + sep + tail + "\n#undef m_vectors\n"
 
@@ -629,6 +668,45 @@ if os.path.exists(pke_src):
                 "            return res;\n"
                 "    }\n"
                 "    DCRTPoly cTilda0(paramsQlP, Format::EVALUATION, true);\n", "keyswitch-hybrid.cpp")
-    os.makedirs(os.path.join(out, "_pke_src"), exist_ok=True)
-    open(os.path.join(out, "_pke_src", "keyswitch-hybrid.cpp"), "w").write(text)
+    sig = ("        if ((addFirst) || (k > 0)) {\n"
+           "            auto cMult = cv[k].TimesNoCheck(cryptoParams->GetPModq());\n")
+    text = once(text, sig,
+                "        if (((addFirst) || (k > 0)) && DCRTPoly::PimExtendTimes(cv[k], cryptoParams->GetPModq(), paramsQlP, resultElements[k]))\n"
+                "            continue;      // B200 intercept: c * [P]_q extended by zero towers, on the device copy\n"
+                "        if ((addFirst) || (k > 0)) {\n"
+                "            auto cMult = cv[k].TimesNoCheck(cryptoParams->GetPModq());\n", "keyswitch-hybrid.cpp")
+    os.makedirs(os.path.join(out, "_pke_src", "keyswitch"), exist_ok=True)
+    open(os.path.join(out, "_pke_src", "keyswitch", "keyswitch-hybrid.cpp"), "w").write(text)
+    # EvalFastRotationExt (ckksrns-leveledshe.cpp:402-460): the addFirst term built the same way
+    rel2 = os.path.join("scheme", "ckksrns", "ckksrns-leveledshe.cpp")
+    text = open(os.path.join(ref, "src", "pke", "lib", rel2)).read()
+    sig = ("        DCRTPoly psiC0       = DCRTPoly(paramsQlP, Format::EVALUATION, true);\n"
+           "        auto cMult           = ciphertext->GetElements()[0].TimesNoCheck(cryptoParams->GetPModq());\n"
+           "        for (usint i = 0; i < sizeQl; i++) {\n"
+           "            psiC0.SetElementAtIndex(i, cMult.GetElementAtIndex(i));\n"
+           "        }\n")
+    text = once(text, sig,
+                "        DCRTPoly psiC0;\n"
+                "        if (!DCRTPoly::PimExtendTimes(ciphertext->GetElements()[0], cryptoParams->GetPModq(), paramsQlP, psiC0)) {      // B200 intercept\n"
+                "            psiC0      = DCRTPoly(paramsQlP, Format::EVALUATION, true);\n"
+                "            auto cMult = ciphertext->GetElements()[0].TimesNoCheck(cryptoParams->GetPModq());\n"
+                "            for (usint i = 0; i < sizeQl; i++) {\n"
+                "                psiC0.SetElementAtIndex(i, cMult.GetElementAtIndex(i));\n"
+                "            }\n"
+                "        }\n", "ckksrns-leveledshe.cpp")
+    # reading a tower's modulus must not fetch the tower: X.GetElementAtIndex(i).GetModulus() -> the same value from the
+    # parameters (ckksrns-leveledshe.cpp:167,216,310,334; bfvrns-leveledshe.cpp:240,462,772,813,858)
+    import re
+    mod_rx = re.compile(r"(\b\w+(?:\[\d+\])?)\.GetElementAtIndex\((\w+)\)\.GetModulus\(\)")
+    text, nsub = mod_rx.subn(r"\1.GetParams()->GetParams()[\2]->GetModulus()", text)
+    if nsub != 4:
+        raise SystemExit(f"hook_patch: expected 4 modulus lookups in ckksrns-leveledshe.cpp, found {nsub}")
+    os.makedirs(os.path.join(out, "_pke_src", "scheme", "ckksrns"), exist_ok=True)
+    open(os.path.join(out, "_pke_src", rel2), "w").write(text)
+    rel3 = os.path.join("scheme", "bfvrns", "bfvrns-leveledshe.cpp")
+    text, nsub = mod_rx.subn(r"\1.GetParams()->GetParams()[\2]->GetModulus()", open(os.path.join(ref, "src", "pke", "lib", rel3)).read())
+    if nsub != 5:
+        raise SystemExit(f"hook_patch: expected 5 modulus lookups in bfvrns-leveledshe.cpp, found {nsub}")
+    os.makedirs(os.path.join(out, "_pke_src", "scheme", "bfvrns"), exist_ok=True)
+    open(os.path.join(out, "_pke_src", rel3), "w").write(text)
 print("hook_patch: patched header tree in", out)

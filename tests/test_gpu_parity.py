@@ -566,3 +566,37 @@ def test_ntt_ws_full_size_round_trip_property(pkg, backend, oracle):
     assert backend.checksum(a, words) == before and backend.checksum(b, words) == before
     backend.free(a); backend.free(b)
     ring.close()
+
+
+@pytest.mark.parametrize("logn,towers,batch", [(4, 3, 2), (11, 8, 3), (14, 30, 1), (16, 4, 2)])
+def test_dcrt_op_scalars_vs_numpy(pkg, backend, oracle, logn, towers, batch):
+    """fhe_dcrt_op_scalars: DCRTPolyImpl::Plus / Minus(std::vector<Integer>) (dcrtpoly-impl.h:556-563, 577-584) - one
+    constant per tower, reduced first as NativeVector::ModAdd / ModSub do, on every coefficient; in place and out of place."""
+    n = 1 << logn
+    q, psi = params(oracle, 60, n, towers)
+    ring = pkg.Ring(backend, n, q, psi)
+    rng = np.random.default_rng(900 + logn)
+    x = rand_polys(rng, batch, n, q)
+    x[0, :, 0] = q - 1
+    x[0, :, 1] = 0
+    s = rng.integers(0, 1 << 63, size=towers, dtype=np.uint64) * np.uint64(2) + np.uint64(1)      # larger than the moduli
+    s[0] = 0
+    words = ring.words(batch)
+    da, dd = backend.alloc(words * 8), backend.alloc(words * 8)
+    backend.h2d(da, x)
+    L = pkg._native.lib
+    qi = [int(v) for v in q]
+    for op, f in ((pkg.OP_ADD, lambda v, c, m: (v + c) % m), (pkg.OP_SUB, lambda v, c, m: (v - c) % m)):
+        want = np.empty_like(x)
+        for t in range(towers):
+            c = int(s[t]) % qi[t]
+            want[:, t, :] = np.array([[f(int(v), c, qi[t]) for v in row] for row in x[:, t, :min(n, 64)]], np.uint64) if n <= 64 else \
+                ((x[:, t, :].astype(object) + (c if op == pkg.OP_ADD else -c)) % qi[t]).astype(np.uint64)
+        pkg._native.check(L.fhe_dcrt_op_scalars(ring.h, op, dd, da, s.ctypes.data_as(ctypes.c_void_p), batch, 0))
+        assert np.array_equal(backend.d2h(dd, words).reshape(x.shape), want)
+        backend.d2d(dd, da, words * 8)
+        pkg._native.check(L.fhe_dcrt_op_scalars(ring.h, op, dd, dd, s.ctypes.data_as(ctypes.c_void_p), batch, 0))
+        assert np.array_equal(backend.d2h(dd, words).reshape(x.shape), want), "in place"
+    assert L.fhe_dcrt_op_scalars(ring.h, pkg.OP_MUL, dd, da, s.ctypes.data_as(ctypes.c_void_p), batch, 0) != 0
+    backend.free(da); backend.free(dd)
+    ring.close()

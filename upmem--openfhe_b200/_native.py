@@ -45,6 +45,7 @@ SIGNATURES = {
     "fhe_ring_towers": (u32, [vp]),
     "fhe_ring_table": (ci, [vp, u32, ci, vp]),
     "fhe_dcrt_op": (ci, [vp, ci, u64, u64, u64, sz, ci]),
+    "fhe_dcrt_op_scalars": (ci, [vp, ci, u64, u64, vp, sz, ci]),
     "fhe_ntt_forward": (ci, [vp, u64, sz, ci]),
     "fhe_ntt_inverse": (ci, [vp, u64, sz, ci]),
     "fhe_ntt_algo": (ci, [vp, u64, sz, ci, ci, ci]),

@@ -77,6 +77,44 @@ ew_ring_kernel(u64* dst, const u64* a, const u64* b,
     }
 }
 
+// dst = a (+|-) s_tower: one constant per tower added to (subtracted from) every coefficient — DCRTPolyImpl::Plus /
+// Minus(const std::vector<Integer>&) (dcrtpoly-impl.h:556-563, 577-584; CKKS EvalAdd / EvalSub with a real constant).  The
+// constants (already reduced) travel in the launch parameters.
+struct TowerScalars { u64 s[EW_SCALARS_MAX]; };
+template <int OP>
+__global__ void __launch_bounds__(EW_THREADS)
+ew_tower_scalar_kernel(u64* dst, const u64* a, size_t nvec, u32 logN, u32 T, const TowerMod* __restrict__ mods, TowerScalars sc) {
+    const ulonglong2* av = reinterpret_cast<const ulonglong2*>(a);
+    ulonglong2* dv = reinterpret_cast<ulonglong2*>(dst);
+    for (size_t v = (size_t)blockIdx.x * EW_THREADS + threadIdx.x; v < nvec; v += (size_t)gridDim.x * EW_THREADS) {
+        const u32 tw = (u32)(((2 * v) >> logN) % T);
+        const u64 q = mods[tw].q, s = sc.s[tw];
+        ulonglong2 x = av[v];
+        x.x = OP == EW_ADD ? addmod(x.x, s, q) : submod(x.x, s, q);
+        x.y = OP == EW_ADD ? addmod(x.y, s, q) : submod(x.y, s, q);
+        dv[v] = x;
+    }
+}
+
+cudaError_t launch_tower_scalars(const RingDev& r, int op, uint64_t* dst, const uint64_t* a, const uint64_t* scalars, size_t batch,
+                                 cudaStream_t st) {
+    const size_t total = batch * r.T * (size_t)r.N;
+    if (total == 0) return cudaSuccess;
+    if (r.T > EW_SCALARS_MAX || r.N < 2 || (op != EW_ADD && op != EW_SUB)) return cudaErrorInvalidValue;
+    if ((((uintptr_t)dst | (uintptr_t)a)) & 15) return cudaErrorMisalignedAddress;
+    TowerScalars sc;
+    for (uint32_t i = 0; i < r.T; i++) sc.s[i] = scalars[i];
+    const size_t nvec = total / 2;
+    size_t g = (nvec + EW_THREADS - 1) / EW_THREADS;
+    const unsigned grid = (unsigned)(g > 148 * 32 ? 148 * 32 : g);
+    u64* d = reinterpret_cast<u64*>(dst);
+    const u64* pa = reinterpret_cast<const u64*>(a);
+    if (op == EW_ADD) ew_tower_scalar_kernel<EW_ADD><<<grid, EW_THREADS, 0, st>>>(d, pa, nvec, r.logN, r.T, r.mods, sc);
+    else ew_tower_scalar_kernel<EW_SUB><<<grid, EW_THREADS, 0, st>>>(d, pa, nvec, r.logN, r.T, r.mods, sc);
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
+}
+
 // Ciphertext tensor product (LeveledSHEBase::EvalMultCore, 2 x 2 case, base-leveledshe.cpp:667-672):
 //   c0 = a0*b0, c1 = a1*b0 + a0*b1, c2 = a1*b1   per tower, per coefficient.
 // One pass instead of four multiplies and an add: 56 B of HBM traffic per coefficient slot instead of

@@ -24,6 +24,10 @@ enum EwOp { EW_ADD = 0, EW_SUB = 1, EW_MUL = 2 };
 // dst = a (op) b over [batch][T][N]; dst may alias a or b.
 cudaError_t launch_elementwise(const RingDev& r, int op, uint64_t* dst, const uint64_t* a,
                                const uint64_t* b, size_t batch, cudaStream_t st);
+// dst = a (op) scalars[tower] over [batch][T][N] (op EW_ADD / EW_SUB; scalars on the host, reduced; T <= EW_SCALARS_MAX)
+#define EW_SCALARS_MAX 64
+cudaError_t launch_tower_scalars(const RingDev& r, int op, uint64_t* dst, const uint64_t* a, const uint64_t* scalars, size_t batch,
+                                 cudaStream_t st);
 // c0 = a0*b0, c1 = a1*b0 + a0*b1, c2 = a1*b1 over [batch][T][N]; outputs may alias inputs element-for-element.
 cudaError_t launch_tensor_product(const RingDev& r, uint64_t* c0, uint64_t* c1, uint64_t* c2,
                                   const uint64_t* a0, const uint64_t* a1, const uint64_t* b0, const uint64_t* b1,

@@ -634,6 +634,23 @@ extern "C" int fhe_dcrt_op(fhe_ring* r, int op, fhe_dptr dst, fhe_dptr a, fhe_dp
     return FHE_OK;
 }
 
+extern "C" int fhe_dcrt_op_scalars(fhe_ring* r, int op, fhe_dptr dst, fhe_dptr a, const uint64_t* scalars, size_t batch, int stream) {
+    StreamRef s;
+    int rc = ring_stream(r, stream, &s);
+    if (rc) return rc;
+    if (op != FHE_OP_ADD && op != FHE_OP_SUB) return fail(FHE_EINVAL, "fhe_dcrt_op_scalars: op must be FHE_OP_ADD or FHE_OP_SUB");
+    if (!scalars) return fail(FHE_EINVAL, "fhe_dcrt_op_scalars: null scalars");
+    if (batch == 0) return FHE_OK;
+    if (!dst || !a) return fail(FHE_EINVAL, "fhe_dcrt_op_scalars: null device pointer");
+    if ((dst | a) & 15) return fail(FHE_EINVAL, "fhe_dcrt_op_scalars: device pointers must be 16-byte aligned");
+    if (r->dev.T > EW_SCALARS_MAX) return fail(FHE_EUNSUPPORTED, "fhe_dcrt_op_scalars: more than %d towers", EW_SCALARS_MAX);
+    if (r->dev.N < 2) return fail(FHE_EUNSUPPORTED, "fhe_dcrt_op_scalars: N must be at least 2");
+    uint64_t red[EW_SCALARS_MAX];
+    for (uint32_t i = 0; i < r->dev.T; i++) red[i] = scalars[i] % r->q[i];          // NativeVector::ModAdd / ModSub reduce the scalar first
+    CUDA_TRY(launch_tower_scalars(r->dev, op, (uint64_t*)(uintptr_t)dst, (const uint64_t*)(uintptr_t)a, red, batch, s));
+    return FHE_OK;
+}
+
 extern "C" int fhe_ntt_algo(fhe_ring* r, fhe_dptr x, size_t batch, int inverse, int algo, int stream) {
     StreamRef s;
     int rc = ring_stream(r, stream, &s);
