@@ -93,8 +93,10 @@ enum { FHE_KERNEL_BOOT = 0, FHE_KERNEL_MOD_ADD = 1, FHE_KERNEL_MOD_MULT = 2, FHE
 /* ---- runtime ------------------------------------------------------------------------------ */
 const char* fhe_last_error(void);
 const char* fhe_version(void);
-/* opts: "key=value,..."; keys: streams (default 4), arena_mb (arena slab size, default 256),
- * chunk_mb (bytes per operand per chunk of the host-operand pipelines, default 32). */
+/* opts: "key=value,..."; keys: streams (default 4), arena_mb (arena slab size, default 256), arena_grow_mb (how much the
+ * arena reserves before an allocation that finds no free block waits for blocks freed behind unfinished work instead of
+ * taking another slab; default a quarter of the device's memory), chunk_mb (bytes per operand per chunk of the
+ * host-operand pipelines, default 32). */
 int fhe_init(int device, const char* opts, fhe_ctx** out);
 int fhe_shutdown(fhe_ctx* ctx);
 int fhe_device(const fhe_ctx* ctx);

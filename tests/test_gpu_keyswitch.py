@@ -44,6 +44,44 @@ def test_keyswitch_hybrid_vs_oracle(pkg, backend, oracle, logn, size_ql, size_p,
     ring.close()
 
 
+@pytest.mark.parametrize("logn,size_ql,size_p,alpha,t", [(11, 6, 2, 2, 0), (15, 5, 2, 2, 65537)])
+def test_keyswitch_hybrid_replayed(pkg, backend, oracle, logn, size_ql, size_p, alpha, t):
+    """The same plan called again and again: the first call runs its launches directly, the second records them (a captured
+    graph per key, csrc/runtime.cu keyswitch_graphed), later ones replay.  Fresh inputs, fresh outputs, a second key, a
+    larger batch (the plan's buffers move) and the first key again: every call bit-equal to the oracle."""
+    n, T = 1 << logn, size_ql + size_p
+    q, psi = oracle.gen_params(58, n, T)
+    qlp = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q, psi)
+    ks = pkg.KeySwitch(ring, size_ql, alpha)
+    npart = ks.digits
+    keys = []
+    for seed in (401, 402):
+        kb, ka = oracle.fill_ring(npart, n, q, seed), oracle.fill_ring(npart, n, q, seed + 50)
+        db, da = backend.alloc(kb.nbytes), backend.alloc(ka.nbytes)
+        backend.h2d(db, kb); backend.h2d(da, ka)
+        keys.append((kb, ka, db, da))
+    launches = []
+    for call, (which, batch) in enumerate([(0, 1), (0, 1), (0, 1), (1, 1), (0, 1), (0, 2), (0, 2), (1, 2), (0, 1)]):
+        kb, ka, db, da = keys[which]
+        c = oracle.fill_ring(batch, n, q[:size_ql].copy(), 500 + call)
+        dc, o0, o1 = backend.alloc(c.nbytes), backend.alloc(c.nbytes), backend.alloc(c.nbytes)
+        backend.h2d(dc, c)
+        before = pkg._native.lib.fhe_launch_count()
+        ks(o0, o1, dc, db, da, batch, t)
+        launches.append(pkg._native.lib.fhe_launch_count() - before)
+        want = oracle.keyswitch_hybrid(qlp, size_ql, alpha, c, kb, ka, t)
+        assert np.array_equal(backend.d2h(o0, c.size).reshape(c.shape), want[0]), f"ct0, call {call}"
+        assert np.array_equal(backend.d2h(o1, c.size).reshape(c.shape), want[1]), f"ct1, call {call}"
+        for pbuf in (dc, o0, o1):
+            backend.free(pbuf)
+    assert launches[1] == launches[0] == launches[2] == launches[4], launches      # a replay counts its kernels like a direct run
+    for _, _, db, da in keys:
+        backend.free(db); backend.free(da)
+    ks.close()
+    ring.close()
+
+
 def test_keyswitch_argument_checks(pkg, backend, oracle):
     n = 64
     q, psi = oracle.gen_params(60, n, 4)

@@ -51,6 +51,52 @@ extern "C" const char* fhe_version(void) { return "fhe_b200 0.1 (sm_100a)"; }
 extern "C" long fhe_launch_count(void) { return kernel_launch_count(); }
 
 // ---------------------------------------------------------------------------------------------
+// capture gate.  While one thread records a CUDA graph on its stream (keyswitch_graphed), nothing else in the process may
+// synchronise the device or that stream, or record an event on it (the arena's markers do, on every stream that carried
+// work): such calls fail and invalidate the capture.  Every API call therefore runs "inside" the gate (GateHold, also held
+// by StreamRef); a capture steps out, waits until it is alone, records, and lets the others back in.  Captures are rare
+// (once per plan and key), so the others spin for some tens of microseconds at most.  Re-entrant per thread.
+// ---------------------------------------------------------------------------------------------
+namespace {
+struct CaptureGate {
+    std::atomic<int> inside{0};
+    std::atomic<int> capturing{0};
+    std::mutex one;
+    static int& depth() { static thread_local int d = 0; return d; }
+    void enter() {
+        if (depth()++) return;
+        for (;;) {
+            while (capturing.load(std::memory_order_acquire)) std::this_thread::yield();
+            inside.fetch_add(1, std::memory_order_acq_rel);
+            if (!capturing.load(std::memory_order_acquire)) return;
+            inside.fetch_sub(1, std::memory_order_acq_rel);
+        }
+    }
+    void leave() {
+        if (--depth() == 0) inside.fetch_sub(1, std::memory_order_release);
+    }
+    void begin_capture() {                         // the caller is inside (it holds a StreamRef)
+        inside.fetch_sub(1, std::memory_order_acq_rel);
+        one.lock();
+        capturing.store(1, std::memory_order_release);
+        while (inside.load(std::memory_order_acquire) != 0) std::this_thread::yield();
+    }
+    void end_capture() {
+        inside.fetch_add(1, std::memory_order_acq_rel);
+        capturing.store(0, std::memory_order_release);
+        one.unlock();
+    }
+};
+CaptureGate g_gate;
+struct GateHold {
+    GateHold() { g_gate.enter(); }
+    ~GateHold() { g_gate.leave(); }
+    GateHold(const GateHold&) = delete;
+    GateHold& operator=(const GateHold&) = delete;
+};
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
 // device arena: slabs obtained with cudaMalloc, first-fit free list with coalescing inside a slab.
 // Takes the place of DpuMemory's 64 MB / 4 KB block map (pim/DpuMemory.h:11-82), sized for HBM.
 // ---------------------------------------------------------------------------------------------
@@ -69,7 +115,8 @@ struct Arena {
     std::vector<Slab> slabs;
     std::map<uintptr_t, std::pair<int, size_t>> live;   // ptr -> (slab, length)
     size_t slab_bytes = 256ull << 20;
-    size_t reserved = 0, in_use = 0;
+    size_t grow_limit = 0;                         // bytes the arena may reserve before it prefers waiting to growing
+    size_t reserved = 0, in_use = 0, stalls = 0;
 
     int alloc(size_t bytes, void** out) {
         if (bytes == 0) bytes = ARENA_ALIGN;
@@ -91,14 +138,20 @@ struct Arena {
                 }
             }
             if (pass == 2) break;
-            if (pass == 0) {                       // blocks parked behind unfinished work: wait for it rather than grow
+            // No free block.  Below grow_limit a new slab is taken: waiting for the parked blocks instead would stall the
+            // host behind everything the device has queued, on every allocation of a loop whose working set is a little
+            // larger than the arena (seen as a 5x cliff between N = 2^15 and 2^16 in the scheme-level runs).  Above it,
+            // the blocks parked behind unfinished work are waited for first.
+            const bool may_grow = reserved + std::max(slab_bytes, bytes) <= grow_limit;
+            if ((pass == 0) != may_grow) {
                 if (parked.empty()) continue;
                 cudaDeviceSynchronize();
                 flush_locked();
+                stalls++;
                 continue;
             }
             Slab sl;
-            sl.size = std::max(slab_bytes, bytes);
+            sl.size = std::max(std::max(slab_bytes, bytes), std::min(reserved / 2, (size_t)2 << 30) / ARENA_ALIGN * ARENA_ALIGN);
             cudaError_t e = cudaMalloc((void**)&sl.base, sl.size);
             if (e != cudaSuccess) {
                 cudaGetLastError();
@@ -228,6 +281,7 @@ struct StreamRef {
     cudaStream_t st = nullptr;
     fhe_ctx* ctx = nullptr;
     int slot = -1;
+    GateHold gate;                                 // see CaptureGate
     StreamRef() = default;
     StreamRef(fhe_ctx* c, int pool_index) : st(c->streams[pool_index]), ctx(c), slot(pool_index) {}
     StreamRef(const StreamRef&) = delete;
@@ -250,6 +304,7 @@ static int get_stream(fhe_ctx* ctx, int stream, StreamRef* out) {
 
 // fhe_free and every internal release of a block that launches may still be using: see Arena::parked.
 static int arena_park(fhe_ctx* ctx, void* p) {
+    GateHold gate_;
     if (!p) return FHE_OK;
     Arena& A = ctx->arena;
     std::lock_guard<std::mutex> lk(A.mu);
@@ -295,6 +350,7 @@ static long opt_value(const char* opts, const char* key, long dflt) {
 // runtime
 // ---------------------------------------------------------------------------------------------
 extern "C" int fhe_init(int device, const char* opts, fhe_ctx** out) {
+    GateHold gate_;
     if (!out) return fail(FHE_EINVAL, "fhe_init: out is null");
     *out = nullptr;
     int n = 0;
@@ -317,6 +373,9 @@ extern "C" int fhe_init(int device, const char* opts, fhe_ctx** out) {
     ctx->epoch.reset(new std::atomic<uint64_t>[ns + 1]);
     for (long i = 0; i <= ns; i++) ctx->epoch[i].store(0);
     ctx->arena.slab_bytes = (size_t)std::max(1l, opt_value(opts, "arena_mb", 256)) << 20;
+    long grow_mb = (long)(prop.totalGlobalMem >> 22);        // default: a quarter of the device
+    if (const char* e = getenv("FHE_B200_ARENA_GROW_MB")) grow_mb = atol(e);
+    ctx->arena.grow_limit = (size_t)std::max(0l, opt_value(opts, "arena_grow_mb", grow_mb)) << 20;
     ctx->chunk_bytes = (size_t)std::max(1l, std::min(1024l, opt_value(opts, "chunk_mb", 32))) << 20;
     for (long i = 0; i < ns; i++) {
         cudaStream_t s;
@@ -332,6 +391,7 @@ extern "C" int fhe_init(int device, const char* opts, fhe_ctx** out) {
 }
 
 extern "C" int fhe_shutdown(fhe_ctx* ctx) {
+    GateHold gate_;
     if (!ctx) return FHE_OK;
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
@@ -347,6 +407,7 @@ extern "C" int fhe_device(const fhe_ctx* ctx) { return ctx ? ctx->device : -1; }
 extern "C" int fhe_num_streams(const fhe_ctx* ctx) { return ctx ? (int)ctx->streams.size() : 0; }
 
 extern "C" int fhe_sync(fhe_ctx* ctx, int stream) {
+    GateHold gate_;
     if (!ctx) return fail(FHE_EINVAL, "null context");
     CUDA_TRY(cudaSetDevice(ctx->device));
     if (stream == -2) { CUDA_TRY(cudaDeviceSynchronize()); return FHE_OK; }
@@ -361,6 +422,7 @@ extern "C" int fhe_sync(fhe_ctx* ctx, int stream) {
 // memory
 // ---------------------------------------------------------------------------------------------
 extern "C" int fhe_alloc(fhe_ctx* ctx, size_t bytes, fhe_dptr* out) {
+    GateHold gate_;
     if (!ctx || !out) return fail(FHE_EINVAL, "fhe_alloc: null argument");
     CUDA_TRY(cudaSetDevice(ctx->device));
     void* p = nullptr;
@@ -371,6 +433,7 @@ extern "C" int fhe_alloc(fhe_ctx* ctx, size_t bytes, fhe_dptr* out) {
 }
 
 extern "C" int fhe_free(fhe_ctx* ctx, fhe_dptr p) {
+    GateHold gate_;
     if (!ctx) return fail(FHE_EINVAL, "null context");
     if (!p) return FHE_OK;
     cudaSetDevice(ctx->device);
@@ -386,6 +449,7 @@ extern "C" int fhe_arena_stats(fhe_ctx* ctx, size_t* reserved_bytes, size_t* in_
 }
 
 extern "C" int fhe_host_alloc(fhe_ctx* ctx, size_t bytes, void** out) {
+    GateHold gate_;
     if (!ctx || !out) return fail(FHE_EINVAL, "fhe_host_alloc: null argument");
     CUDA_TRY(cudaSetDevice(ctx->device));
     CUDA_TRY(cudaMallocHost(out, bytes ? bytes : 1));
@@ -395,6 +459,7 @@ extern "C" int fhe_host_alloc(fhe_ctx* ctx, size_t bytes, void** out) {
 }
 
 extern "C" int fhe_host_free(fhe_ctx* ctx, void* p) {
+    GateHold gate_;
     if (!ctx) return fail(FHE_EINVAL, "null context");
     if (!p) return FHE_OK;
     {
@@ -431,6 +496,7 @@ extern "C" int fhe_d2d(fhe_ctx* ctx, fhe_dptr dst, fhe_dptr src, size_t bytes, i
 // timing
 // ---------------------------------------------------------------------------------------------
 extern "C" int fhe_timer_start(fhe_ctx* ctx, int stream) {
+    GateHold gate_;
     StreamRef s;
     int rc = get_stream(ctx, stream, &s);
     if (rc) return rc;
@@ -446,6 +512,7 @@ extern "C" int fhe_timer_start(fhe_ctx* ctx, int stream) {
 }
 
 extern "C" int fhe_timer_stop(fhe_ctx* ctx, int stream, float* elapsed_ms) {
+    GateHold gate_;
     StreamRef s;
     int rc = get_stream(ctx, stream, &s);
     if (rc) return rc;
@@ -498,6 +565,7 @@ static TowerMod make_mod(uint64_t q) {
 }
 
 extern "C" int fhe_ring_destroy(fhe_ring* r) {
+    GateHold gate_;
     if (!r) return FHE_OK;
     fhe_ctx* c = r->ctx;
     cudaSetDevice(c->device);
@@ -512,6 +580,7 @@ extern "C" int fhe_ring_destroy(fhe_ring* r) {
 
 extern "C" int fhe_ring_create(fhe_ctx* ctx, uint32_t N, uint32_t T, const uint64_t* q, const uint64_t* psi,
                                fhe_ring** out) {
+    GateHold gate_;
     if (!ctx || !q || !out) return fail(FHE_EINVAL, "fhe_ring_create: null argument");
     *out = nullptr;
     if (N == 0 || (N & (N - 1)) || N > 65536) return fail(FHE_EINVAL, "fhe_ring_create: N=%u must be a power of two <= 65536", N);
@@ -598,6 +667,7 @@ extern "C" uint32_t fhe_ring_n(const fhe_ring* r) { return r ? r->dev.N : 0; }
 extern "C" uint32_t fhe_ring_towers(const fhe_ring* r) { return r ? r->dev.T : 0; }
 
 extern "C" int fhe_ring_table(const fhe_ring* r, uint32_t tower, int which, uint64_t* out) {
+    GateHold gate_;
     if (!r || !out) return fail(FHE_EINVAL, "fhe_ring_table: null argument");
     if (!r->has_ntt) return fail(FHE_EINVAL, "fhe_ring_table: ring has no NTT tables");
     if (tower >= r->dev.T || which < 0 || which > 3) return fail(FHE_EINVAL, "fhe_ring_table: bad tower/table");
@@ -691,6 +761,7 @@ extern "C" int fhe_automorphism(fhe_ring* r, fhe_dptr dst, fhe_dptr src, size_t 
 }
 
 extern "C" int fhe_precompute_automap(uint32_t N, uint32_t k, uint32_t* map) {
+    GateHold gate_;
     if (!map) return fail(FHE_EINVAL, "fhe_precompute_automap: null output");
     if (N == 0 || (N & (N - 1))) return fail(FHE_EINVAL, "fhe_precompute_automap: N must be a power of two");
     uint32_t logn = 0;
@@ -852,6 +923,7 @@ extern "C" int fhe_checksum(fhe_ctx* ctx, fhe_dptr src, size_t nwords, uint64_t*
 // legacy descriptor path (PimData::common_do_ops, pim/PimData.h:275-305)
 // ---------------------------------------------------------------------------------------------
 extern "C" int fhe_launch(fhe_ctx* ctx, int kernel_id, const void* desc, fhe_dptr heap_base) {
+    GateHold gate_;
     if (!ctx || !desc) return fail(FHE_EINVAL, "fhe_launch: null argument");
     if (kernel_id == FHE_KERNEL_BOOT) return FHE_OK;          // boot only reset the DPU heap
     int op;
@@ -891,6 +963,7 @@ extern "C" int fhe_launch(fhe_ctx* ctx, int kernel_id, const void* desc, fhe_dpt
 // RNS basis conversion and scaling
 // ---------------------------------------------------------------------------------------------
 extern "C" int fhe_ring_view(fhe_ring* parent, uint32_t first, uint32_t count, fhe_ring** out) {
+    GateHold gate_;
     if (!parent || !out) return fail(FHE_EINVAL, "fhe_ring_view: null argument");
     *out = nullptr;
     if (count == 0 || first + count > parent->dev.T || first + count < first)
@@ -918,6 +991,7 @@ struct Scratch {
     size_t bytes = 0;
     int need(fhe_ctx* ctx, size_t n) {
         if (n <= bytes) return FHE_OK;
+        GateHold gate_;
         if (p) { cudaDeviceSynchronize(); arena_park(ctx, p); p = nullptr; bytes = 0; }
         int rc = ctx->arena.alloc(n, &p);
         if (rc) return rc;
@@ -929,6 +1003,7 @@ struct Scratch {
 
 template <class T>
 int upload(fhe_ctx* ctx, const std::vector<T>& h, void** d) {
+    GateHold gate_;
     if (!*d) {
         int rc = ctx->arena.alloc(std::max<size_t>(h.size() * sizeof(T), 16), d);
         if (rc) return rc;
@@ -1023,6 +1098,7 @@ bool fhe::basis_tc_build(const uint64_t* hat, uint32_t sq, uint32_t sp, uint32_t
 }
 
 extern "C" int fhe_basis_destroy(fhe_basis* b) {
+    GateHold gate_;
     if (!b) return FHE_OK;
     cudaSetDevice(b->ctx->device);
     cudaDeviceSynchronize();
@@ -1036,6 +1112,7 @@ extern "C" int fhe_basis_destroy(fhe_basis* b) {
 
 extern "C" int fhe_basis_create(fhe_ring* from, fhe_ring* to, const uint64_t* qhat_inv_modq, const uint64_t* qhat_modp,
                                 fhe_basis** out) {
+    GateHold gate_;
     if (!from || !to || !out) return fail(FHE_EINVAL, "fhe_basis_create: null argument");
     *out = nullptr;
     if (from->ctx != to->ctx) return fail(FHE_EINVAL, "fhe_basis_create: rings live on different contexts");
@@ -1167,16 +1244,12 @@ extern "C" int fhe_approx_mod_up(fhe_basis* b, fhe_dptr dst_qp, fhe_dptr src_q, 
     return FHE_OK;
 }
 
-extern "C" int fhe_approx_mod_down(fhe_basis* b, fhe_dptr dst_q, fhe_dptr src_qp, size_t batch, uint64_t t, int stream) {
-    if (!b) return fail(FHE_EINVAL, "null basis");
-    StreamRef s;
-    int rc = ring_stream(b->from, stream, &s);
-    if (rc) return rc;
-    if (batch == 0) return FHE_OK;
-    if (!dst_q || !src_qp) return fail(FHE_EINVAL, "fhe_approx_mod_down: null device pointer");
-    if ((dst_q | src_qp) & 15) return fail(FHE_EINVAL, "fhe_approx_mod_down: device pointers must be 16-byte aligned");
+// ApproxModDown in three steps, so that a composition can run the middle one over several polys at once and from a captured
+// graph (fhe_keyswitch_hybrid): the tables, P part -> the correction term over Q in EVALUATION form, the final subtraction.
+static int mod_down_tables(fhe_basis* b, uint64_t t, cudaStream_t s, BasisDev* out) {
     fhe_ring *P = b->from, *Q = b->to;                      // the basis switches P -> Q
-    const uint32_t N = P->dev.N, logN = P->dev.logN, sp = b->dev.sq, sq = b->dev.sp;
+    const uint32_t sq = b->dev.sp;
+    int rc;
     if (!b->pinv_ready) {                                    // [P^-1]_{q_i}, rns-cryptoparameters.cpp:190-197
         std::vector<ulonglong4> k(sq);
         for (uint32_t i = 0; i < sq; i++) {
@@ -1203,18 +1276,45 @@ extern "C" int fhe_approx_mod_down(fhe_basis* b, fhe_dptr dst_q, fhe_dptr src_qp
         bd.pre = (const ulonglong2*)b->d_pre_t;
         bd.tgt = (const BasisTarget*)b->d_tgt_t;
     }
+    *out = bd;
+    return FHE_OK;
+}
+
+// sw[batch][sq][N] <- the P towers of src[batch][sq+sp][N] taken to COEFFICIENT form (:1150-1151), switched to Q
+// (:1152-1159, :1170-1171) and back to EVALUATION (:1172); partP[batch][sp][N] is scratch
+static int mod_down_inner(fhe_basis* b, const BasisDev& bd, uint64_t* sw, uint64_t* partP, const uint64_t* src, size_t batch, cudaStream_t s) {
+    fhe_ring *P = b->from, *Q = b->to;
+    const uint32_t N = P->dev.N, logN = P->dev.logN, sp = b->dev.sq, sq = b->dev.sp;
+    int rc;
+    if ((rc = ring_ntt(P, partP, batch, true, s, "fhe_approx_mod_down", src + (size_t)sq * N, sp, sq + sp))) return rc;
+    CUDA_TRY(launch_basis_switch(bd, sw, sq, 0, partP, sp, 0, batch, logN, false, s));
+    return ring_ntt(Q, sw, batch, false, s, "fhe_approx_mod_down");
+}
+
+// dst = (src's Q towers - sw) * [P^-1]_q (:1173)
+static int mod_down_final(fhe_basis* b, uint64_t* dst, const uint64_t* src, const uint64_t* sw, size_t batch, cudaStream_t s) {
+    const uint32_t sp = b->dev.sq, sq = b->dev.sp;
+    CUDA_TRY(launch_tower_affine(0, dst, src, sw, batch, b->from->dev.logN, sq, sq + sp, b->to->dev.mods, (const ulonglong4*)b->d_pinv, s));
+    return FHE_OK;
+}
+
+extern "C" int fhe_approx_mod_down(fhe_basis* b, fhe_dptr dst_q, fhe_dptr src_qp, size_t batch, uint64_t t, int stream) {
+    if (!b) return fail(FHE_EINVAL, "null basis");
+    StreamRef s;
+    int rc = ring_stream(b->from, stream, &s);
+    if (rc) return rc;
+    if (batch == 0) return FHE_OK;
+    if (!dst_q || !src_qp) return fail(FHE_EINVAL, "fhe_approx_mod_down: null device pointer");
+    if ((dst_q | src_qp) & 15) return fail(FHE_EINVAL, "fhe_approx_mod_down: device pointers must be 16-byte aligned");
+    const uint32_t N = b->from->dev.N, sp = b->dev.sq, sq = b->dev.sp;
+    BasisDev bd;
+    if ((rc = mod_down_tables(b, t, s, &bd))) return rc;
     uint64_t* dst = (uint64_t*)(uintptr_t)dst_q;
     const uint64_t* src = (const uint64_t*)(uintptr_t)src_qp;
     const size_t wq = batch * sq * (size_t)N, wp = batch * sp * (size_t)N;
     if ((rc = b->s0.need(b->ctx, wp * 8)) || (rc = b->s1.need(b->ctx, wq * 8))) return rc;
-    uint64_t* partP = (uint64_t*)b->s0.p;
-    uint64_t* sw = (uint64_t*)b->s1.p;
-    if ((rc = ring_ntt(P, partP, batch, true, s, "fhe_approx_mod_down", src + (size_t)sq * N, sp, sq + sp))) return rc;   // :1150-1151
-    CUDA_TRY(launch_basis_switch(bd, sw, sq, 0, partP, sp, 0, batch, logN, false, s));                // :1152-1159, :1170-1171
-    if ((rc = ring_ntt(Q, sw, batch, false, s, "fhe_approx_mod_down"))) return rc;             // :1172
-    CUDA_TRY(launch_tower_affine(0, dst, src, sw, batch, logN, sq, sq + sp, Q->dev.mods,       // :1173
-                                 (const ulonglong4*)b->d_pinv, s));
-    return FHE_OK;
+    if ((rc = mod_down_inner(b, bd, (uint64_t*)b->s1.p, (uint64_t*)b->s0.p, src, batch, s))) return rc;
+    return mod_down_final(b, dst, src, (const uint64_t*)b->s1.p, batch, s);
 }
 
 struct fhe_rescale {
@@ -1229,6 +1329,7 @@ struct fhe_rescale {
 };
 
 extern "C" int fhe_rescale_destroy(fhe_rescale* p) {
+    GateHold gate_;
     if (!p) return FHE_OK;
     cudaSetDevice(p->ctx->device);
     cudaDeviceSynchronize();
@@ -1243,6 +1344,7 @@ extern "C" int fhe_rescale_destroy(fhe_rescale* p) {
 }
 
 extern "C" int fhe_rescale_create(fhe_ring* ring, const uint64_t* qlql, const uint64_t* qlinv, fhe_rescale** out) {
+    GateHold gate_;
     if (!ring || !out) return fail(FHE_EINVAL, "fhe_rescale_create: null argument");
     *out = nullptr;
     const uint32_t T = ring->dev.T;
@@ -1455,6 +1557,7 @@ struct fhe_tower_scale {
 };
 
 extern "C" int fhe_tower_scale_destroy(fhe_tower_scale* p) {
+    GateHold gate_;
     if (!p) return FHE_OK;
     cudaSetDevice(p->ctx->device);
     cudaDeviceSynchronize();
@@ -1464,6 +1567,7 @@ extern "C" int fhe_tower_scale_destroy(fhe_tower_scale* p) {
 }
 
 extern "C" int fhe_tower_scale_create(fhe_ring* ring, const uint64_t* c, fhe_tower_scale** out) {
+    GateHold gate_;
     if (!ring || !c || !out) return fail(FHE_EINVAL, "fhe_tower_scale_create: null argument");
     *out = nullptr;
     CUDA_TRY(cudaSetDevice(ring->ctx->device));
@@ -1521,6 +1625,7 @@ struct fhe_scale_round {
 };
 
 extern "C" int fhe_scale_round_destroy(fhe_scale_round* p) {
+    GateHold gate_;
     if (!p) return FHE_OK;
     cudaSetDevice(p->ctx->device);
     cudaDeviceSynchronize();
@@ -1532,6 +1637,7 @@ extern "C" int fhe_scale_round_destroy(fhe_scale_round* p) {
 
 extern "C" int fhe_scale_round_create(fhe_ring* ring, uint32_t size_out, int out_last, const double* frac, const uint64_t* modo,
                                       fhe_scale_round** out) {
+    GateHold gate_;
     if (!ring || !frac || !modo || !out) return fail(FHE_EINVAL, "fhe_scale_round_create: null argument");
     *out = nullptr;
     const uint32_t T = ring->dev.T;
@@ -1619,6 +1725,7 @@ struct HostPipe {
 
 extern "C" int fhe_dcrt_multi_op_host(fhe_ring* r, const int* ops, int nops, uint64_t* const* dsts,
                                       const uint64_t* a, const uint64_t* b, size_t batch) {
+    GateHold gate_;
     if (!r) return fail(FHE_EINVAL, "null ring");
     if (!ops || !dsts || nops < 1 || nops > 4) return fail(FHE_EINVAL, "fhe_dcrt_multi_op_host: need 1..4 ops");
     for (int i = 0; i < nops; i++) {
@@ -1659,6 +1766,7 @@ extern "C" int fhe_dcrt_multi_op_host(fhe_ring* r, const int* ops, int nops, uin
 }
 
 extern "C" int fhe_dcrt_chain_host(fhe_ring* r, const int* ops, int nops, uint64_t* a, const uint64_t* b, size_t batch) {
+    GateHold gate_;
     if (!r) return fail(FHE_EINVAL, "null ring");
     if (!ops || nops < 1 || nops > 8) return fail(FHE_EINVAL, "fhe_dcrt_chain_host: need 1..8 ops");
     bool any_ntt = false, any_ew = false;
@@ -1700,6 +1808,7 @@ extern "C" int fhe_dcrt_op_host(fhe_ring* r, int op, uint64_t* dst, const uint64
 }
 
 extern "C" int fhe_ntt_host(fhe_ring* r, uint64_t* x, size_t batch, int inverse) {
+    GateHold gate_;
     if (!r) return fail(FHE_EINVAL, "null ring");
     if (r->ntt_identity || batch == 0 || r->dev.N == 1) return FHE_OK;
     if (!r->has_ntt) return fail(FHE_EINVAL, "fhe_ntt_host: ring was created without roots of unity");
@@ -1830,6 +1939,7 @@ extern "C" int fhe_deserialize(fhe_ring* r, fhe_dptr dst, const void* src_host, 
 // diagnostics
 // ---------------------------------------------------------------------------------------------
 extern "C" int fhe_imad_probe(fhe_ctx* ctx, int blocks, int threads, int iters, float* elapsed_ms) {
+    GateHold gate_;
     if (!ctx) return fail(FHE_EINVAL, "null context");
     if (blocks < 1 || threads < 1 || threads > 1024 || iters < 1) return fail(FHE_EINVAL, "fhe_imad_probe: bad launch shape");
     CUDA_TRY(cudaSetDevice(ctx->device));
@@ -1863,6 +1973,7 @@ struct fhe_decrypt_scale {
 };
 
 extern "C" int fhe_decrypt_scale_destroy(fhe_decrypt_scale* p) {
+    GateHold gate_;
     if (!p) return FHE_OK;
     cudaSetDevice(p->ctx->device);
     if (p->d_k) arena_park(p->ctx, p->d_k);
@@ -1873,6 +1984,7 @@ extern "C" int fhe_decrypt_scale_destroy(fhe_decrypt_scale* p) {
 
 extern "C" int fhe_decrypt_scale_create(fhe_ring* ring, uint64_t t, const uint64_t* modt, const uint64_t* b_modt,
                                         const double* frac, const double* b_frac, fhe_decrypt_scale** out) {
+    GateHold gate_;
     if (!ring || !out) return fail(FHE_EINVAL, "fhe_decrypt_scale_create: null argument");
     *out = nullptr;
     if (t < 2 || t >= (1ull << 60)) return fail(FHE_EINVAL, "fhe_decrypt_scale_create: plaintext modulus %llu not in [2, 2^60)", (unsigned long long)t);
@@ -1975,10 +2087,22 @@ struct fhe_keyswitch {
     };
     std::vector<Part> parts;
     fhe_basis* p_to_ql = nullptr;                 // ApproxModDown
-    Scratch coef, digits, c0, c1;
+    Scratch coef, digits, c01;                    // c01: both halves of the inner product, [2][batch][T][N]
+    // fhe_keyswitch_hybrid's middle (everything between the first read of c and the last write of ct0/ct1 touches only the
+    // plan's own buffers and the key) as captured graphs, one per (batch, key, t, buffer addresses)
+    struct Graph {
+        std::vector<uint64_t> key;
+        cudaGraphExec_t exec = nullptr;
+        int kernels = 0;
+        uint64_t used = 0;
+    };
+    std::vector<Graph> graphs;
+    uint64_t tick = 0;
+    bool warmed = false, graph_off = false;
 };
 
 extern "C" int fhe_keyswitch_destroy(fhe_keyswitch* k) {
+    GateHold gate_;
     if (!k) return FHE_OK;
     cudaSetDevice(k->ctx->device);
     cudaDeviceSynchronize();
@@ -1988,12 +2112,15 @@ extern "C" int fhe_keyswitch_destroy(fhe_keyswitch* k) {
     }
     fhe_basis_destroy(k->p_to_ql);
     fhe_ring_destroy(k->ql); fhe_ring_destroy(k->p);
-    k->coef.drop(k->ctx); k->digits.drop(k->ctx); k->c0.drop(k->ctx); k->c1.drop(k->ctx);
+    for (auto& g : k->graphs)
+        if (g.exec) cudaGraphExecDestroy(g.exec);
+    k->coef.drop(k->ctx); k->digits.drop(k->ctx); k->c01.drop(k->ctx);
     delete k;
     return FHE_OK;
 }
 
 extern "C" int fhe_keyswitch_create(fhe_ring* ring_qlp, uint32_t size_ql, uint32_t alpha, fhe_keyswitch** out) {
+    GateHold gate_;
     if (!ring_qlp || !out) return fail(FHE_EINVAL, "fhe_keyswitch_create: null argument");
     *out = nullptr;
     const uint32_t T = ring_qlp->dev.T;
@@ -2027,30 +2154,45 @@ extern "C" int fhe_keyswitch_create(fhe_ring* ring_qlp, uint32_t size_ql, uint32
 
 extern "C" uint32_t fhe_keyswitch_digits(const fhe_keyswitch* k) { return k ? (uint32_t)k->parts.size() : 0; }
 
-// EvalKeySwitchPrecomputeCore (keyswitch-hybrid.cpp:330-420) on stream s: digits [np][batch][T][N]
-static int keyswitch_precompute(fhe_keyswitch* k, uint64_t* digits, const uint64_t* c, size_t batch, cudaStream_t s) {
+// EvalKeySwitchPrecomputeCore (keyswitch-hybrid.cpp:330-420) on stream s: digits [np][batch][T][N], in two steps.
+// keyswitch_read: the only launches that read c - its towers to COEFFICIENT form, one transform for all digits
+// (:392-393), and each digit's own stored towers copied where they belong (:410-412).
+static int keyswitch_read(fhe_keyswitch* k, uint64_t* digits, const uint64_t* c, size_t batch, cudaStream_t s) {
+    const uint32_t N = k->qlp->dev.N, T = k->qlp->dev.T;
+    int rc;
+    if ((rc = ring_ntt(k->ql, (uint64_t*)k->coef.p, batch, true, s, "fhe_keyswitch_precompute", c, k->size_ql, k->size_ql))) return rc;
+    for (size_t j = 0; j < k->parts.size(); j++) {
+        auto& P = k->parts[j];
+        CUDA_TRY(copy_towers(digits + j * batch * (size_t)T * N, T, P.s, c, k->size_ql, P.s, P.e - P.s, batch, N, s));
+    }
+    return FHE_OK;
+}
+// keyswitch_extend: ApproxSwitchCRTBasis of every digit to its complement basis (:396-402), written where the towers belong
+// in the digit, then EVALUATION (:404) in place there.  Reads and writes the plan's buffers only.
+static int keyswitch_extend(fhe_keyswitch* k, uint64_t* digits, size_t batch, cudaStream_t s) {
     const uint32_t N = k->qlp->dev.N, logN = k->qlp->dev.logN, T = k->qlp->dev.T;
     const char* who = "fhe_keyswitch_precompute";
+    const uint64_t* coef = (const uint64_t*)k->coef.p;
     int rc;
-    if ((rc = k->coef.need(k->ctx, batch * std::min(k->alpha, k->size_ql) * (size_t)N * 8))) return rc;
-    uint64_t* coef = (uint64_t*)k->coef.p;
     for (size_t j = 0; j < k->parts.size(); j++) {
         auto& P = k->parts[j];
         const uint32_t sp = P.e - P.s;
         uint64_t* d = digits + j * batch * (size_t)T * N;
-        // the digit's towers, COEFFICIENT (:392-393): read where they lie in c, packed into the scratch
-        if ((rc = ring_ntt(P.part, coef, batch, true, s, who, c + (size_t)P.s * N, sp, k->size_ql))) return rc;
-        // ApproxSwitchCRTBasis to the complement basis (:396-402), written where the towers belong in the digit, then
-        // EVALUATION (:404) in place there
         if (P.lo) {
-            CUDA_TRY(launch_basis_switch(P.to_lo->dev, d, T, 0, coef, sp, 0, batch, logN, false, s));
+            CUDA_TRY(launch_basis_switch(P.to_lo->dev, d, T, 0, coef, k->size_ql, P.s, batch, logN, false, s));
             if ((rc = ring_ntt(P.lo, d, batch, false, s, who, nullptr, T))) return rc;
         }
-        CUDA_TRY(launch_basis_switch(P.to_hi->dev, d, T, P.e, coef, sp, 0, batch, logN, false, s));
+        CUDA_TRY(launch_basis_switch(P.to_hi->dev, d, T, P.e, coef, k->size_ql, P.s, batch, logN, false, s));
         if ((rc = ring_ntt(P.hi, d + (size_t)P.e * N, batch, false, s, who, nullptr, T))) return rc;
-        CUDA_TRY(copy_towers(d, T, P.s, c, k->size_ql, P.s, sp, batch, N, s));      // the digit's own stored towers (:410-412)
+        (void)sp;
     }
     return FHE_OK;
+}
+static int keyswitch_precompute(fhe_keyswitch* k, uint64_t* digits, const uint64_t* c, size_t batch, cudaStream_t s) {
+    int rc;
+    if ((rc = k->coef.need(k->ctx, batch * k->size_ql * (size_t)k->qlp->dev.N * 8))) return rc;
+    if ((rc = keyswitch_read(k, digits, c, batch, s))) return rc;
+    return keyswitch_extend(k, digits, batch, s);
 }
 
 extern "C" int fhe_keyswitch_precompute(fhe_keyswitch* k, fhe_dptr digits, fhe_dptr c, size_t batch, int stream) {
@@ -2079,6 +2221,65 @@ extern "C" int fhe_keyswitch_inner(fhe_keyswitch* k, fhe_dptr ctilda0, fhe_dptr 
     return FHE_OK;
 }
 
+// Runs `body` (launches on s that touch nothing but plan-owned buffers and the addresses in `key`) from a captured graph:
+// the first call of a plan runs it directly (function attributes, lazily built tables), the first call with a new key
+// captures it, later ones replay it with one driver call.  FHE_B200_KS_GRAPH=0 turns this off.
+template <class Body>
+static int keyswitch_graphed(fhe_keyswitch* k, const std::vector<uint64_t>& key, cudaStream_t s, Body body) {
+    // 0: never, 1 (default): where the launches cost more than the kernels (measured: up to 2^20 words per poly over Ql u P;
+    // beyond that the replay is a few percent slower than direct launches from 16 host threads), 2: always
+    static const int mode = [] { const char* e = getenv("FHE_B200_KS_GRAPH"); return e && e[0] >= '0' && e[0] <= '2' ? e[0] - '0' : 1; }();
+    const bool launch_bound = key[0] * k->qlp->dev.T * (uint64_t)k->qlp->dev.N <= (1ull << 20);
+    if (mode == 0 || (mode == 1 && !launch_bound) || k->graph_off || !k->warmed || s == cudaStreamLegacy || s == nullptr) {
+        k->warmed = true;
+        return body();
+    }
+    for (auto& g : k->graphs)
+        if (g.key == key) {
+            g.used = ++k->tick;
+            CUDA_TRY(cudaGraphLaunch(g.exec, s));
+            kernel_launch_count_add(g.kernels);
+            return FHE_OK;
+        }
+    g_gate.begin_capture();                                  // alone in the library from here (CaptureGate)
+    if (cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed) != cudaSuccess) {
+        g_gate.end_capture();
+        cudaGetLastError();
+        k->graph_off = true;
+        return body();
+    }
+    const int rc = body();                                   // recorded, not run (the launchers count their kernels here)
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamEndCapture(s, &graph);
+    g_gate.end_capture();
+    cudaGraphExec_t exec = nullptr;
+    size_t nodes = 0;
+    if (!rc && e == cudaSuccess && graph) {
+        e = cudaGraphGetNodes(graph, nullptr, &nodes);
+        if (e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
+    }
+    if (graph) cudaGraphDestroy(graph);
+    if (rc) return rc;
+    if (e != cudaSuccess || !exec) {
+        cudaGetLastError();
+        k->graph_off = true;
+        return body();
+    }
+    if (k->graphs.size() >= 64) {                            // least recently used out
+        size_t v = 0;
+        for (size_t i = 1; i < k->graphs.size(); i++)
+            if (k->graphs[i].used < k->graphs[v].used) v = i;
+        CUDA_TRY(cudaStreamSynchronize(s));
+        cudaGraphExecDestroy(k->graphs[v].exec);
+        k->graphs.erase(k->graphs.begin() + v);
+    }
+    fhe_keyswitch::Graph g;
+    g.key = key; g.exec = exec; g.kernels = (int)nodes; g.used = ++k->tick;
+    k->graphs.push_back(g);
+    CUDA_TRY(cudaGraphLaunch(exec, s));
+    return FHE_OK;
+}
+
 extern "C" int fhe_keyswitch_hybrid(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1, fhe_dptr c, fhe_dptr evk_b, fhe_dptr evk_a,
                                     size_t batch, uint64_t t, int stream) {
     if (!k) return fail(FHE_EINVAL, "null key-switching plan");
@@ -2086,21 +2287,37 @@ extern "C" int fhe_keyswitch_hybrid(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1
     if (!ct0 || !ct1 || !c || !evk_b || !evk_a) return fail(FHE_EINVAL, "fhe_keyswitch_hybrid: null device pointer");
     if (ct0 == ct1) return fail(FHE_EINVAL, "fhe_keyswitch_hybrid: the two outputs must be distinct");
     if ((ct0 | ct1 | c | evk_b | evk_a) & 15) return fail(FHE_EINVAL, "fhe_keyswitch_hybrid: device pointers must be 16-byte aligned");
-    const size_t item = (size_t)k->qlp->dev.T * k->qlp->dev.N * 8;
+    const uint32_t N = k->qlp->dev.N, T = k->qlp->dev.T, sq = k->size_ql, sp = k->size_p;
+    const size_t item = (size_t)T * N;                       // words of one poly over Ql u P
+    fhe_basis* md = k->p_to_ql;
+    StreamRef s;
     int rc;
-    if ((rc = k->digits.need(k->ctx, k->parts.size() * batch * item)) || (rc = k->c0.need(k->ctx, batch * item)) ||
-        (rc = k->c1.need(k->ctx, batch * item)))
+    if ((rc = ring_stream(k->qlp, stream, &s))) return rc;
+    if ((rc = k->coef.need(k->ctx, batch * sq * (size_t)N * 8)) || (rc = k->digits.need(k->ctx, k->parts.size() * batch * item * 8)) ||
+        (rc = k->c01.need(k->ctx, 2 * batch * item * 8)) || (rc = md->s0.need(k->ctx, 2 * batch * sp * (size_t)N * 8)) ||
+        (rc = md->s1.need(k->ctx, 2 * batch * sq * (size_t)N * 8)))
         return rc;
-    {
-        StreamRef s;
-        if ((rc = ring_stream(k->qlp, stream, &s))) return rc;
-        if ((rc = keyswitch_precompute(k, (uint64_t*)k->digits.p, (const uint64_t*)(uintptr_t)c, batch, s))) return rc;
-        CUDA_TRY(launch_ks_inner(k->qlp->dev, (uint64_t*)k->c0.p, (uint64_t*)k->c1.p, (const uint64_t*)k->digits.p,
-                                 (const uint64_t*)(uintptr_t)evk_b, (const uint64_t*)(uintptr_t)evk_a, (uint32_t)k->parts.size(), batch, s));
-    }
-    // EvalFastKeySwitchCore (:430-440): both halves back to Ql
-    if ((rc = fhe_approx_mod_down(k->p_to_ql, ct0, (fhe_dptr)(uintptr_t)k->c0.p, batch, t, stream))) return rc;
-    return fhe_approx_mod_down(k->p_to_ql, ct1, (fhe_dptr)(uintptr_t)k->c1.p, batch, t, stream);
+    BasisDev bd;
+    if ((rc = mod_down_tables(md, t, s, &bd))) return rc;
+    uint64_t *digits = (uint64_t*)k->digits.p, *c01 = (uint64_t*)k->c01.p, *sw = (uint64_t*)md->s1.p, *partP = (uint64_t*)md->s0.p;
+    // 1. the launches that read c
+    if ((rc = keyswitch_read(k, digits, (const uint64_t*)(uintptr_t)c, batch, s))) return rc;
+    // 2. digits over Ql u P, the inner product with the key (EvalFastKeySwitchCoreExt, :442-480), and ApproxModDown's
+    //    correction term of both halves at once (EvalFastKeySwitchCore, :430-440)
+    const std::vector<uint64_t> key = {batch, t, evk_b, evk_a, (uint64_t)(uintptr_t)k->coef.p, (uint64_t)(uintptr_t)digits,
+                                       (uint64_t)(uintptr_t)c01, (uint64_t)(uintptr_t)sw, (uint64_t)(uintptr_t)partP,
+                                       (uint64_t)(uintptr_t)bd.pre, (uint64_t)(uintptr_t)bd.tgt};
+    rc = keyswitch_graphed(k, key, s, [&]() -> int {
+        int r = keyswitch_extend(k, digits, batch, s);
+        if (r) return r;
+        CUDA_TRY(launch_ks_inner(k->qlp->dev, c01, c01 + batch * item, digits, (const uint64_t*)(uintptr_t)evk_b,
+                                 (const uint64_t*)(uintptr_t)evk_a, (uint32_t)k->parts.size(), batch, s));
+        return mod_down_inner(md, bd, sw, partP, c01, 2 * batch, s);
+    });
+    if (rc) return rc;
+    // 3. the launches that write the results
+    if ((rc = mod_down_final(md, (uint64_t*)(uintptr_t)ct0, c01, sw, batch, s))) return rc;
+    return mod_down_final(md, (uint64_t*)(uintptr_t)ct1, c01 + batch * item, sw + batch * sq * (size_t)N, batch, s);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -2114,6 +2331,7 @@ struct fhe_crt_decomp {
 };
 
 extern "C" int fhe_crt_decompose_destroy(fhe_crt_decomp* p) {
+    GateHold gate_;
     if (!p) return FHE_OK;
     cudaSetDevice(p->ctx->device);
     cudaDeviceSynchronize();
@@ -2124,6 +2342,7 @@ extern "C" int fhe_crt_decompose_destroy(fhe_crt_decomp* p) {
 }
 
 extern "C" int fhe_crt_decompose_create(fhe_ring* ring, fhe_crt_decomp** out) {
+    GateHold gate_;
     if (!ring || !out) return fail(FHE_EINVAL, "fhe_crt_decompose_create: null argument");
     *out = nullptr;
     if (ring->dev.N < 2) return fail(FHE_EUNSUPPORTED, "fhe_crt_decompose_create: N must be at least 2");
@@ -2192,6 +2411,7 @@ struct fhe_behz {
 };
 
 extern "C" int fhe_behz_destroy(fhe_behz* z) {
+    GateHold gate_;
     if (!z) return FHE_OK;
     cudaSetDevice(z->ctx->device);
     cudaDeviceSynchronize();
@@ -2207,6 +2427,7 @@ extern "C" int fhe_behz_destroy(fhe_behz* z) {
 static uint64_t prod_all_mod(const std::vector<uint64_t>& f, uint64_t m) { return prod_mod(f, (size_t)-1, m); }
 
 extern "C" int fhe_behz_create(fhe_ring* ring_qbsk, uint32_t size_q, uint64_t t, fhe_behz** out) {
+    GateHold gate_;
     if (!ring_qbsk || !out) return fail(FHE_EINVAL, "fhe_behz_create: null argument");
     *out = nullptr;
     const uint32_t T = ring_qbsk->dev.T;
@@ -2521,6 +2742,7 @@ extern "C" int fhe_comm_unique_id(void* id, size_t cap) {
 }
 
 extern "C" int fhe_comm_create(fhe_ctx* ctx, int nranks, int rank, const void* id, fhe_comm** out) {
+    GateHold gate_;
     if (!ctx || !id || !out) return fail(FHE_EINVAL, "fhe_comm_create: null argument");
     *out = nullptr;
     if (nranks < 1 || rank < 0 || rank >= nranks) return fail(FHE_EINVAL, "fhe_comm_create: rank %d not in [0,%d)", rank, nranks);
@@ -2538,6 +2760,7 @@ extern "C" int fhe_comm_create(fhe_ctx* ctx, int nranks, int rank, const void* i
 }
 
 extern "C" int fhe_comm_destroy(fhe_comm* c) {
+    GateHold gate_;
     if (!c) return FHE_OK;
     NcclApi* api = nccl_api();
     if (api && c->comm) { cudaSetDevice(c->ctx->device); api->CommDestroy(c->comm); }
@@ -2569,6 +2792,7 @@ struct fhe_group_ring {
 };
 
 extern "C" int fhe_group_destroy(fhe_group* g) {
+    GateHold gate_;
     if (!g) return FHE_OK;
     NcclApi* api = nccl_api();
     for (size_t i = 0; i < g->comms.size(); i++)
@@ -2579,6 +2803,7 @@ extern "C" int fhe_group_destroy(fhe_group* g) {
 }
 
 extern "C" int fhe_group_create(int ndev, const int* devices, const char* opts, fhe_group** out) {
+    GateHold gate_;
     if (!out) return fail(FHE_EINVAL, "fhe_group_create: out is null");
     *out = nullptr;
     int have = 0;
@@ -2628,6 +2853,7 @@ extern "C" int fhe_group_partition(const fhe_group* g, size_t batch, int rank, s
 // Legacy descriptor on every device at once: the descriptor's sizes are per device (PimData divides them by
 // getNumDpus(), pim/PimData.h:281-290), heap_bases[rank] is that device's heap.  Blocking, like start_kernel().
 extern "C" int fhe_group_launch(fhe_group* g, int kernel_id, const void* desc, const fhe_dptr* heap_bases) {
+    GateHold gate_;
     if (!g || !desc || !heap_bases) return fail(FHE_EINVAL, "fhe_group_launch: null argument");
     const size_t n = g->ctx.size();
     if (n == 1) return fhe_launch(g->ctx[0], kernel_id, desc, heap_bases[0]);
@@ -2646,6 +2872,7 @@ extern "C" int fhe_group_launch(fhe_group* g, int kernel_id, const void* desc, c
 }
 
 extern "C" int fhe_group_ring_destroy(fhe_group_ring* r) {
+    GateHold gate_;
     if (!r) return FHE_OK;
     for (fhe_ring* x : r->rings) fhe_ring_destroy(x);
     delete r;
@@ -2654,6 +2881,7 @@ extern "C" int fhe_group_ring_destroy(fhe_group_ring* r) {
 
 extern "C" int fhe_group_ring_create(fhe_group* g, uint32_t N, uint32_t towers, const uint64_t* q, const uint64_t* psi,
                                      fhe_group_ring** out) {
+    GateHold gate_;
     if (!g || !out) return fail(FHE_EINVAL, "fhe_group_ring_create: null argument");
     *out = nullptr;
     auto* r = new fhe_group_ring;
@@ -2745,6 +2973,7 @@ extern "C" int fhe_group_gather(fhe_group_ring* r, uint64_t* host, const fhe_dpt
 // (north_star: "NCCL over NVLink only to gather results").  ncclAllGather when the blocks are equal, grouped
 // ncclSend / ncclRecv otherwise.  Enqueued on `stream` of every device; complete after fhe_group_sync.
 extern "C" int fhe_group_all_gather(fhe_group_ring* r, const fhe_dptr* dst, const fhe_dptr* src, size_t batch, int stream) {
+    GateHold gate_;
     if (!r || !dst || !src) return fail(FHE_EINVAL, "fhe_group_all_gather: null argument");
     fhe_group* g = r->g;
     const int n = (int)g->ctx.size();
@@ -2806,6 +3035,7 @@ extern "C" int fhe_group_all_gather(fhe_group_ring* r, const fhe_dptr* dst, cons
 // The in-place operator sequence on HOST operands over all devices: each device streams its block of the batch through
 // its own pipeline (fhe_dcrt_chain_host), one host thread per device.  Blocking.
 extern "C" int fhe_group_chain_host(fhe_group_ring* r, const int* ops, int nops, uint64_t* a, const uint64_t* b, size_t batch) {
+    GateHold gate_;
     if (!r) return fail(FHE_EINVAL, "null group ring");
     const int n = (int)r->rings.size();
     if (n == 1) return fhe_dcrt_chain_host(r->rings[0], ops, nops, a, b, batch);
