@@ -383,6 +383,41 @@ inline bool resident_binary(PimManager *pim, const Towers &a, std::shared_ptr<Re
   return true;
 }
 
+/* a device copy of the given shape with no contents yet; the caller launches into it on stream S */
+inline std::shared_ptr<Resident> fresh_resident(const std::shared_ptr<PimRing> &ring, fhe_ctx *ctx, int S, size_t towers, size_t n) {
+  auto r = std::make_shared<Resident>();
+  r->ring = ring;
+  r->ctx = ctx;
+  r->stream = S;
+  r->towers = towers;
+  r->n = n;
+  PimManager::check(fhe_alloc(ctx, towers * n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
+  r->device_newer = true;
+  return r;
+}
+
+/* LeveledSHEBase::EvalMultCore, the 2 x 2 case (src/pke/lib/schemebase/base-leveledshe.cpp:667-672, and the same
+ * products in LeveledSHEBFVRNS::EvalMult, bfvrns-leveledshe.cpp:324-336): (a0*b0, a0*b1 + a1*b0, a1*b1) as ONE launch
+ * (fhe_ct_tensor_product) into three fresh device copies, instead of two polynomial copies, four Times and a +=. */
+template <class Towers>
+inline bool resident_tensor_product(PimManager *pim, const Towers &a0, std::shared_ptr<Resident> &ra0, const Towers &a1,
+                                    std::shared_ptr<Resident> &ra1, const Towers &b0, std::shared_ptr<Resident> &rb0, const Towers &b1,
+                                    std::shared_ptr<Resident> &rb1, std::shared_ptr<Resident> (&out)[3]) {
+  if (!pim || a0.empty() || a1.size() != a0.size() || b0.size() != a0.size() || b1.size() != a0.size()) return false;
+  auto d0 = ensure_device(pim, a0, ra0), d1 = ensure_device(pim, a1, ra1);
+  auto e0 = (&b0 == &a0) ? d0 : ensure_device(pim, b0, rb0), e1 = (&b1 == &a1) ? d1 : ensure_device(pim, b1, rb1);
+  if (d1->ring != d0->ring || e0->ring != d0->ring || e1->ring != d0->ring) return false;      /* same moduli, same ring object */
+  fhe_ctx *ctx = d0->ctx;
+  const int S = hook_stream(ctx);
+  std::shared_ptr<Resident> r[3];
+  for (auto &x : r) x = fresh_resident(d0->ring, ctx, S, d0->towers, d0->n);
+  const fhe_dptr c[3] = {r[0]->d, r[1]->d, r[2]->d}, a[2] = {d0->d, d1->d}, b[2] = {e0->d, e1->d};
+  PimManager::check(fhe_ct_tensor_product(d0->ring->handle(), c, a, b, 1, S), "pim hook: tensor product");
+  finish(ctx);
+  for (int i = 0; i < 3; i++) out[i] = r[i];
+  return true;
+}
+
 template <class Towers>
 inline bool resident_switch_format(PimManager *pim, const Towers &a, std::shared_ptr<Resident> &ra, bool to_evaluation) {
   if (!pim || a.empty()) return false;
@@ -1066,17 +1101,6 @@ inline std::shared_ptr<KeyBlock> key_block_for(PimManager *pim, KeyAt key_at, si
   return kb;
 }
 
-inline std::shared_ptr<Resident> fresh_resident(const std::shared_ptr<PimRing> &ring, fhe_ctx *ctx, int S, size_t towers, size_t n) {
-  auto r = std::make_shared<Resident>();
-  r->ring = ring;
-  r->ctx = ctx;
-  r->stream = S;
-  r->towers = towers;
-  r->n = n;
-  PimManager::check(fhe_alloc(ctx, towers * n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
-  r->device_newer = true;
-  return r;
-}
 
 template <class Towers, class KeyAt>
 inline bool resident_keyswitch_hybrid(PimManager *pim, const Towers &c, std::shared_ptr<Resident> &rc, size_t nkeys, KeyAt key_at,

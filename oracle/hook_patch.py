@@ -151,6 +151,24 @@ def patch_class(text):
                 "        ct0.pim = ct1.pim = c.pim;\n"
                 "        return true;\n"
                 "    }\n"
+                "    /* LeveledSHEBase::EvalMultCore, 2 x 2 (base-leveledshe.cpp:667-672): the three products of two ciphertexts' elements\n"
+                "     * as one launch on the device copies */\n"
+                "    static bool PimTensorProduct(const DCRTPolyImpl& a0, const DCRTPolyImpl& a1, const DCRTPolyImpl& b0, const DCRTPolyImpl& b1,\n"
+                "                                 std::vector<DCRTPolyImpl>& out) {\n"
+                "        if (!a0.pim || a0.m_format != Format::EVALUATION || a1.m_format != Format::EVALUATION ||\n"
+                "            b0.m_format != Format::EVALUATION || b1.m_format != Format::EVALUATION || out.size() != 3)\n"
+                "            return false;\n"
+                "        std::shared_ptr<pimhook::Resident> r[3];\n"
+                "        if (!pimhook::resident_tensor_product(a0.pim.get(), a0.m_vectors_, a0.pimres_, a1.m_vectors_, a1.pimres_, b0.m_vectors_,\n"
+                "                                              b0.pimres_, b1.m_vectors_, b1.pimres_, r))\n"
+                "            return false;\n"
+                "        for (int i = 0; i < 3; i++) {\n"
+                "            out[i]         = DCRTPolyImpl(a0.m_params, Format::EVALUATION, false);\n"
+                "            out[i].pimres_ = r[i];\n"
+                "            out[i].pim     = a0.pim;\n"
+                "        }\n"
+                "        return true;\n"
+                "    }\n"
                 "    /* KeySwitchExt / EvalFastRotationExt (keyswitch-hybrid.cpp:231-256, ckksrns-leveledshe.cpp:402-460): c over Ql times\n"
                 "     * per-tower constants, extended by zero towers to paramsExt (Ql u P) - instead of TimesNoCheck + SetElementAtIndex */\n"
                 "    static bool PimExtendTimes(const DCRTPolyImpl& c, const std::vector<NativeInteger>& consts,\n"
@@ -707,6 +725,63 @@ if os.path.exists(pke_src):
     text, nsub = mod_rx.subn(r"\1.GetParams()->GetParams()[\2]->GetModulus()", open(os.path.join(ref, "src", "pke", "lib", rel3)).read())
     if nsub != 5:
         raise SystemExit(f"hook_patch: expected 5 modulus lookups in bfvrns-leveledshe.cpp, found {nsub}")
+    # LeveledSHEBFVRNS::EvalMult's products over the extended basis (bfvrns-leveledshe.cpp:324-336), 2 x 2: one launch
+    text = once(text,
+                "#else\n"
+                "    std::vector<bool> isFirstAdd(cvMultSize, true);\n"
+                "    for (size_t i = 0; i < cv1Size; i++) {\n",
+                "#else\n"
+                "    std::vector<bool> isFirstAdd(cvMultSize, true);\n"
+                "    if (cv1Size == 2 && cv2Size == 2 && DCRTPoly::PimTensorProduct(cv1[0], cv1[1], cv2[0], cv2[1], cvMult))\n"
+                "        cv1Size = 0;      // B200 intercept: done, skip the loops\n"
+                "    for (size_t i = 0; i < cv1Size; i++) {\n", "bfvrns-leveledshe.cpp")
     os.makedirs(os.path.join(out, "_pke_src", "scheme", "bfvrns"), exist_ok=True)
     open(os.path.join(out, "_pke_src", rel3), "w").write(text)
+    # the scheme's bilinear step as one launch, and sums of two ciphertexts without the copy that precedes the in-place form
+    # (base-leveledshe.cpp:591-598, 624-629, 657-672; bfvrns-leveledshe.cpp:324-336)
+    rel4 = os.path.join("schemebase", "base-leveledshe.cpp")
+    text = open(os.path.join(ref, "src", "pke", "lib", rel4)).read()
+    text = once(text,
+                "    std::vector<Element> cv1        = ciphertext1->GetElements();\n"
+                "    const std::vector<Element>& cv2 = ciphertext2->GetElements();\n\n"
+                "    size_t cResultSize = cv1.size() + cv2.size() - 1;\n",
+                "    // B200 intercept: the copy of ciphertext1's elements (the CPU path multiplies two of them in place) only when needed\n"
+                "    const std::vector<Element>& cv1r = ciphertext1->GetElements();\n"
+                "    const std::vector<Element>& cv2  = ciphertext2->GetElements();\n"
+                "    {\n"
+                "        std::vector<Element> dev(3);\n"
+                "        if (cv1r.size() == 2 && cv2.size() == 2 && DCRTPoly::PimTensorProduct(cv1r[0], cv1r[1], cv2[0], cv2[1], dev)) {\n"
+                "            result->SetElements(std::move(dev));\n"
+                "            result->SetNoiseScaleDeg(ciphertext1->GetNoiseScaleDeg() + ciphertext2->GetNoiseScaleDeg());\n"
+                "            result->SetScalingFactor(ciphertext1->GetScalingFactor() * ciphertext2->GetScalingFactor());\n"
+                "            const auto plainMod0 = ciphertext1->GetCryptoParameters()->GetPlaintextModulus();\n"
+                "            result->SetScalingFactorInt(\n"
+                "                ciphertext1->GetScalingFactorInt().ModMul(ciphertext2->GetScalingFactorInt(), plainMod0));\n"
+                "            return result;\n"
+                "        }\n"
+                "    }\n"
+                "    std::vector<Element> cv1 = cv1r;\n\n"
+                "    size_t cResultSize = cv1.size() + cv2.size() - 1;\n", "base-leveledshe.cpp")
+    for name, op in (("Add", "+"), ("Sub", "-")):
+        text = once(text,
+                    "    auto result = ciphertext1->Clone();\n"
+                    f"    Eval{name}CoreInPlace(result, ciphertext2);\n"
+                    "    return result;\n",
+                    "    {   // B200 intercept: out-of-place sums (one launch each on the device copies) instead of a copy and an in-place sum\n"
+                    "        const std::vector<Element>& cv1 = ciphertext1->GetElements();\n"
+                    "        const std::vector<Element>& cv2 = ciphertext2->GetElements();\n"
+                    "        if (ciphertext1->GetPim() == nullptr && !cv1.empty() && cv1.size() == cv2.size()) {\n"
+                    "            auto sum = ciphertext1->CloneZero();\n"
+                    "            std::vector<Element> cv;\n"
+                    "            cv.reserve(cv1.size());\n"
+                    f"            for (size_t i = 0; i < cv1.size(); i++) cv.push_back(cv1[i] {op} cv2[i]);\n"
+                    "            sum->SetElements(std::move(cv));\n"
+                    "            return sum;\n"
+                    "        }\n"
+                    "    }\n"
+                    "    auto result = ciphertext1->Clone();\n"
+                    f"    Eval{name}CoreInPlace(result, ciphertext2);\n"
+                    "    return result;\n", "base-leveledshe.cpp")
+    os.makedirs(os.path.join(out, "_pke_src", "schemebase"), exist_ok=True)
+    open(os.path.join(out, "_pke_src", rel4), "w").write(text)
 print("hook_patch: patched header tree in", out)

@@ -17,6 +17,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <deque>
+#include <functional>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -118,49 +119,67 @@ struct Arena {
     size_t grow_limit = 0;                         // bytes the arena may reserve before it prefers waiting to growing
     size_t reserved = 0, in_use = 0, stalls = 0;
 
+    bool take_locked(size_t bytes, void** out) {
+        for (size_t s = 0; s < slabs.size(); s++) {
+            auto& fl = slabs[s].free_;
+            for (auto it = fl.begin(); it != fl.end(); ++it) {
+                if (it->second < bytes) continue;
+                size_t off = it->first, len = it->second;
+                fl.erase(it);
+                if (len > bytes) fl[off + bytes] = len - bytes;
+                *out = slabs[s].base + off;
+                live[(uintptr_t)*out] = {(int)s, bytes};
+                in_use += bytes;
+                return true;
+            }
+        }
+        return false;
+    }
+
     int alloc(size_t bytes, void** out) {
         if (bytes == 0) bytes = ARENA_ALIGN;
         bytes = (bytes + ARENA_ALIGN - 1) / ARENA_ALIGN * ARENA_ALIGN;
         std::lock_guard<std::mutex> lk(mu);
         if (!parked.empty()) reap_locked();
-        for (int pass = 0; pass < 3; pass++) {
-            for (size_t s = 0; s < slabs.size(); s++) {
-                auto& fl = slabs[s].free_;
-                for (auto it = fl.begin(); it != fl.end(); ++it) {
-                    if (it->second < bytes) continue;
-                    size_t off = it->first, len = it->second;
-                    fl.erase(it);
-                    if (len > bytes) fl[off + bytes] = len - bytes;
-                    *out = slabs[s].base + off;
-                    live[(uintptr_t)*out] = {(int)s, bytes};
-                    in_use += bytes;
-                    return FHE_OK;
-                }
+        bool sealed = false, grown = false, waited = false;
+        for (;;) {
+            if (take_locked(bytes, out)) return FHE_OK;
+            // No free block.  First the blocks freed since the last markers get theirs (see `pending`).  Then, below
+            // grow_limit, a new slab is taken: waiting for the parked blocks instead would stall the host behind
+            // everything the device has queued, on every allocation of a loop whose working set is a little larger than
+            // the arena (seen as a 5x cliff between N = 2^15 and 2^16 in the scheme-level runs).  Above the limit the
+            // blocks parked behind unfinished work are waited for first.
+            if (!sealed && !pending.empty()) {
+                sealed = true;
+                if (seal) seal();
+                reap_locked();
+                continue;
             }
-            if (pass == 2) break;
-            // No free block.  Below grow_limit a new slab is taken: waiting for the parked blocks instead would stall the
-            // host behind everything the device has queued, on every allocation of a loop whose working set is a little
-            // larger than the arena (seen as a 5x cliff between N = 2^15 and 2^16 in the scheme-level runs).  Above it,
-            // the blocks parked behind unfinished work are waited for first.
             const bool may_grow = reserved + std::max(slab_bytes, bytes) <= grow_limit;
-            if ((pass == 0) != may_grow) {
-                if (parked.empty()) continue;
+            const bool can_wait = !waited && (!parked.empty() || !pending.empty());
+            if (!grown && (may_grow || !can_wait)) {
+                grown = true;
+                Slab sl;
+                sl.size = std::max(std::max(slab_bytes, bytes), std::min(reserved / 2, (size_t)2 << 30) / ARENA_ALIGN * ARENA_ALIGN);
+                cudaError_t e = cudaMalloc((void**)&sl.base, sl.size);
+                if (e == cudaSuccess) {
+                    sl.free_[0] = sl.size;
+                    reserved += sl.size;
+                    slabs.push_back(std::move(sl));
+                    continue;
+                }
+                cudaGetLastError();
+                if (!can_wait)
+                    return fail(FHE_ENOMEM, "device arena: cudaMalloc(%zu) failed: %s", sl.size, cudaGetErrorString(e));
+            }
+            if (can_wait) {
+                waited = true;
                 cudaDeviceSynchronize();
                 flush_locked();
                 stalls++;
                 continue;
             }
-            Slab sl;
-            sl.size = std::max(std::max(slab_bytes, bytes), std::min(reserved / 2, (size_t)2 << 30) / ARENA_ALIGN * ARENA_ALIGN);
-            cudaError_t e = cudaMalloc((void**)&sl.base, sl.size);
-            if (e != cudaSuccess) {
-                cudaGetLastError();
-                return fail(FHE_ENOMEM, "device arena: cudaMalloc(%zu) failed: %s", sl.size,
-                            cudaGetErrorString(e));
-            }
-            sl.free_[0] = sl.size;
-            reserved += sl.size;
-            slabs.push_back(std::move(sl));
+            break;
         }
         return fail(FHE_ENOMEM, "device arena: no block of %zu bytes", bytes);
     }
@@ -203,6 +222,12 @@ struct Arena {
     };
     struct Parked { void* p; std::vector<std::shared_ptr<Marker>> waits; };
     std::deque<Parked> parked;
+    // Freed blocks that have no markers yet.  Recording one event per busy stream on every free costs tens of microseconds
+    // under this mutex when sixteen host threads free small blocks; a marker recorded later covers at least as much, so the
+    // frees are collected and sealed together (arena_seal_locked: every 32 blocks or 256 MB, or when alloc finds nothing).
+    std::vector<void*> pending;
+    size_t pending_bytes = 0;
+    std::function<void()> seal;                    // set by fhe_init: needs the context's streams
     std::vector<cudaEvent_t> spare_events;
     struct StreamMark { std::shared_ptr<Marker> last; uint64_t epoch = 0; };
     std::vector<StreamMark> marks;                 // one per stream slot (pool streams, then the legacy stream)
@@ -229,10 +254,15 @@ struct Arena {
     void flush_locked() {                          // after a device-wide synchronisation: nothing is pending any more
         for (auto& pk : parked) release_locked(pk.p);
         parked.clear();
+        for (void* p : pending) release_locked(p);
+        pending.clear();
+        pending_bytes = 0;
     }
 
     void destroy() {
         parked.clear();
+        pending.clear();
+        pending_bytes = 0;
         marks.clear();
         for (cudaEvent_t e : spare_events) cudaEventDestroy(e);
         spare_events.clear();
@@ -302,18 +332,13 @@ static int get_stream(fhe_ctx* ctx, int stream, StreamRef* out) {
     return FHE_OK;
 }
 
-// fhe_free and every internal release of a block that launches may still be using: see Arena::parked.
-static int arena_park(fhe_ctx* ctx, void* p) {
-    GateHold gate_;
-    if (!p) return FHE_OK;
+// markers for everything freed since the last call (Arena::pending); A.mu is held
+static void arena_seal_locked(fhe_ctx* ctx) {
     Arena& A = ctx->arena;
-    std::lock_guard<std::mutex> lk(A.mu);
-    if (A.live.find((uintptr_t)p) == A.live.end()) return fail(FHE_EINVAL, "fhe_free: %p is not a live arena block", p);
-    for (auto& pk : A.parked)
-        if (pk.p == p) return fail(FHE_EINVAL, "fhe_free: %p was already freed", p);
+    if (A.pending.empty()) return;
     const size_t nslots = ctx->streams.size() + 1;
     if (A.marks.size() != nslots) A.marks.resize(nslots);
-    Arena::Parked pk{p, {}};
+    std::vector<std::shared_ptr<Arena::Marker>> waits;
     for (size_t i = 0; i < nslots; i++) {
         uint64_t e = ctx->epoch[i].load(std::memory_order_acquire);
         if (e == 0) continue;                                   // this stream has never carried work
@@ -323,15 +348,36 @@ static int arena_park(fhe_ctx* ctx, void* p) {
             if (!mk) {                                          // cannot record: fall back to waiting for the device
                 cudaDeviceSynchronize();
                 A.flush_locked();
-                return A.release_locked(p);
+                return;
             }
             m.last = mk; m.epoch = e;
         }
-        if (!m.last->finished()) pk.waits.push_back(m.last);
+        if (!m.last->finished()) waits.push_back(m.last);
     }
-    if (pk.waits.empty()) return A.release_locked(p);
-    A.parked.push_back(std::move(pk));
+    for (void* p : A.pending) {
+        if (waits.empty()) A.release_locked(p);
+        else A.parked.push_back(Arena::Parked{p, waits});
+    }
+    A.pending.clear();
+    A.pending_bytes = 0;
     if (A.parked.size() > 64) A.reap_locked();
+}
+
+// fhe_free and every internal release of a block that launches may still be using: see Arena::parked.
+static int arena_park(fhe_ctx* ctx, void* p) {
+    GateHold gate_;
+    if (!p) return FHE_OK;
+    Arena& A = ctx->arena;
+    std::lock_guard<std::mutex> lk(A.mu);
+    auto it = A.live.find((uintptr_t)p);
+    if (it == A.live.end()) return fail(FHE_EINVAL, "fhe_free: %p is not a live arena block", p);
+    for (auto& pk : A.parked)
+        if (pk.p == p) return fail(FHE_EINVAL, "fhe_free: %p was already freed", p);
+    for (void* q : A.pending)
+        if (q == p) return fail(FHE_EINVAL, "fhe_free: %p was already freed", p);
+    A.pending.push_back(p);
+    A.pending_bytes += it->second.second;
+    if (A.pending.size() >= 32 || A.pending_bytes >= ((size_t)256 << 20)) arena_seal_locked(ctx);
     return FHE_OK;
 }
 
@@ -373,6 +419,7 @@ extern "C" int fhe_init(int device, const char* opts, fhe_ctx** out) {
     ctx->epoch.reset(new std::atomic<uint64_t>[ns + 1]);
     for (long i = 0; i <= ns; i++) ctx->epoch[i].store(0);
     ctx->arena.slab_bytes = (size_t)std::max(1l, opt_value(opts, "arena_mb", 256)) << 20;
+    ctx->arena.seal = [ctx] { arena_seal_locked(ctx); };
     long grow_mb = (long)(prop.totalGlobalMem >> 22);        // default: a quarter of the device
     if (const char* e = getenv("FHE_B200_ARENA_GROW_MB")) grow_mb = atol(e);
     ctx->arena.grow_limit = (size_t)std::max(0l, opt_value(opts, "arena_grow_mb", grow_mb)) << 20;
