@@ -16,6 +16,7 @@
 // tower_affine_kernel / rescale_spread_kernel: one pass, 128-bit loads and stores, HBM-bound.
 #include <stdlib.h>
 #include <algorithm>
+#include <atomic>
 #include "modarith.cuh"
 #include "kernels.h"
 
@@ -902,14 +903,28 @@ static cudaError_t launch_basis_switch_tc_t(const BasisDev& bd, u64* d, uint32_t
     const size_t floor_bytes = SUB == 1 ? 80 * 1024 : 116 * 1024;
     if (smem < floor_bytes) smem = floor_bytes;
     if (smem > 227 * 1024) return cudaErrorInvalidValue;
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    auto kern = basis_switch_tc_kernel<EXACT, TPR, SUB>;
+    // The attribute is per function and device, and `smem` depends on the plan: two host threads that set it per launch to
+    // their own sizes can lower it under each other's launch (seen as "invalid argument" from 16 threads).  It only bounds
+    // what a launch may ask for, so it is raised to the device's limit once per device.
+    static std::atomic<unsigned long long> attr_done{0};
+    static std::atomic<int> sm_cache[64];
+    int sms = dev < 64 ? sm_cache[dev].load(std::memory_order_relaxed) : 0;
+    if (dev >= 64 || !((attr_done.load(std::memory_order_acquire) >> dev) & 1) || sms <= 0) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (dev < 64) {
+            sm_cache[dev].store(sms, std::memory_order_relaxed);
+            attr_done.fetch_or(1ull << dev, std::memory_order_release);
+        }
+    }
     const size_t per_group = std::max<size_t>(1, (size_t)(SUB == 1 ? 2 : 1) * sms / bd.tc_groups);
     dim3 grid((unsigned)std::min((tiles + SUB - 1) / SUB, per_group), bd.tc_groups);
-    auto kern = basis_switch_tc_kernel<EXACT, TPR, SUB>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
     kern<<<grid, TC_M * TPR * SUB, smem, st>>>(d, s, (u32)tiles, logN, bd, srcT, src0, dstT, dst0);
     kernel_launch_count_add(1);
     return cudaGetLastError();

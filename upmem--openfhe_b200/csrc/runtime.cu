@@ -211,11 +211,13 @@ struct Arena {
     struct Marker {
         cudaEvent_t ev = nullptr;
         bool done = false;
-        bool finished() {
-            if (!done) {
+        uint64_t asked = 0;                        // the reap pass that last found it unfinished: blocks share markers
+        bool finished(uint64_t pass = 0) {
+            if (!done && !(pass && asked == pass)) {
                 cudaError_t e = cudaEventQuery(ev);
                 if (e == cudaSuccess) done = true;
                 else if (e != cudaErrorNotReady) { cudaGetLastError(); done = true; }   // a dead context frees nothing later either
+                else asked = pass;
             }
             return done;
         }
@@ -242,11 +244,13 @@ struct Arena {
     }
 
     // blocks whose markers have all completed return to the free list (called with mu held)
+    uint64_t reap_pass = 0;
     void reap_locked() {
+        const uint64_t pass = ++reap_pass;
         for (auto it = parked.begin(); it != parked.end();) {
             bool ready = true;
             for (auto& w : it->waits)
-                if (!w->finished()) { ready = false; break; }
+                if (!w->finished(pass)) { ready = false; break; }
             if (ready) { release_locked(it->p); it = parked.erase(it); }
             else ++it;
         }
@@ -377,7 +381,21 @@ static int arena_park(fhe_ctx* ctx, void* p) {
         if (q == p) return fail(FHE_EINVAL, "fhe_free: %p was already freed", p);
     A.pending.push_back(p);
     A.pending_bytes += it->second.second;
-    if (A.pending.size() >= 32 || A.pending_bytes >= ((size_t)256 << 20)) arena_seal_locked(ctx);
+    // how many frees share one set of markers: 32 when many streams are busy (a set costs one event per busy stream), every
+    // free when at most two are (one caller thread: the block is back in the free list as soon as its stream has passed it)
+    static const long fixed = [] { const char* e = getenv("FHE_B200_ARENA_SEAL"); return e ? atol(e) : 0l; }();
+    size_t group = 32;
+    if (fixed > 0) group = (size_t)fixed;
+    else {
+        const size_t nslots = ctx->streams.size() + 1;
+        size_t busy = 0;
+        for (size_t i = 0; i < nslots && busy <= 2; i++) {
+            const uint64_t e = ctx->epoch[i].load(std::memory_order_acquire);
+            if (e != 0 && (i >= A.marks.size() || !A.marks[i].last || A.marks[i].epoch != e)) busy++;
+        }
+        if (busy <= 2) group = 1;
+    }
+    if (A.pending.size() >= group || A.pending_bytes >= ((size_t)256 << 20)) arena_seal_locked(ctx);
     return FHE_OK;
 }
 
