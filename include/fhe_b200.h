@@ -308,8 +308,12 @@ int fhe_scale_and_round_native(fhe_decrypt_scale* plan, fhe_dptr dst, fhe_dptr s
  *   fhe_keyswitch_inner = EvalFastKeySwitchCoreExt (:442-480): ctilda0 = sum_j digits[j] * evk_b[j],
  *       ctilda1 = sum_j digits[j] * evk_a[j], one fused pass; the key polys are given over the towers of ring_qlp
  *       ([digits][T][N], EVALUATION: towers i < size_ql and size_q.. of the scheme's key, :463-476).
- *   fhe_keyswitch_hybrid = KeySwitchCore / EvalFastKeySwitchCore (:324-328, 422-440): the two above, then
- *       ApproxModDown of both halves; ct0, ct1 over Ql [batch][size_ql][N]; t = 0 CKKS, t > 0 BGV. */
+ *   fhe_keyswitch_fast = EvalFastKeySwitchCore (:415-437), what every rotation of a hoisted set calls on the shared
+ *       digits: the inner product above, then ApproxModDown of both halves at once; ct0, ct1 over Ql
+ *       [batch][size_ql][N]; t = 0 CKKS, t > 0 BGV / BFV.
+ *   fhe_keyswitch_hybrid = KeySwitchCore (:324-328) = precompute, then fast.  Between the launches that read c and
+ *       the two that write ct0 / ct1 everything touches the plan's buffers and the key only; that part is replayed
+ *       from a captured CUDA graph where the launches cost more than the kernels (FHE_B200_KS_GRAPH=0 turns it off). */
 typedef struct fhe_keyswitch fhe_keyswitch;
 int fhe_keyswitch_create(fhe_ring* ring_qlp, uint32_t size_ql, uint32_t alpha, fhe_keyswitch** out);
 int fhe_keyswitch_destroy(fhe_keyswitch* plan);
@@ -317,6 +321,8 @@ uint32_t fhe_keyswitch_digits(const fhe_keyswitch* plan);
 int fhe_keyswitch_precompute(fhe_keyswitch* plan, fhe_dptr digits, fhe_dptr c, size_t batch, int stream);
 int fhe_keyswitch_inner(fhe_keyswitch* plan, fhe_dptr ctilda0, fhe_dptr ctilda1, fhe_dptr digits, fhe_dptr evk_b,
                         fhe_dptr evk_a, size_t batch, int stream);
+int fhe_keyswitch_fast(fhe_keyswitch* plan, fhe_dptr ct0, fhe_dptr ct1, fhe_dptr digits, fhe_dptr evk_b, fhe_dptr evk_a,
+                       size_t batch, uint64_t t, int stream);
 int fhe_keyswitch_hybrid(fhe_keyswitch* plan, fhe_dptr ct0, fhe_dptr ct1, fhe_dptr c, fhe_dptr evk_b, fhe_dptr evk_a,
                          size_t batch, uint64_t t, int stream);
 

@@ -1183,7 +1183,10 @@ inline bool resident_keyswitch_digits(PimManager *pim, const Towers &c, std::sha
  * resident_keyswitch_digits returns) are read in place, others are gathered first. */
 template <class Towers, class DigitAt, class KeyAt>
 inline bool resident_keyswitch_inner(PimManager *pim, size_t np, DigitAt digit_at, size_t nkeys, KeyAt key_at, size_t sizeP, size_t alpha,
-                                     const void *key_id, std::shared_ptr<Resident> &r0, std::shared_ptr<Resident> &r1) {
+                                     const void *key_id, std::shared_ptr<Resident> &r0, std::shared_ptr<Resident> &r1,
+                                     bool down = false, uint64_t t = 0) {
+  /* down: EvalFastKeySwitchCore (keyswitch-hybrid.cpp:415-437) - the inner product AND ApproxModDown of both halves as one
+   * call (fhe_keyswitch_fast); the results are over Ql */
   if (!pim || np == 0 || np > nkeys || sizeP == 0 || alpha == 0) return false;
   KeyRef<Towers> d0 = digit_at(0);
   const size_t T = d0.towers.size();
@@ -1221,8 +1224,23 @@ inline bool resident_keyswitch_inner(PimManager *pim, size_t np, DigitAt digit_a
     for (size_t j = 0; j < np; j++) PimManager::check(fhe_d2d(ctx, gathered->p + j * poly, dd[j]->d, poly, S), "pim hook: digit gather");
     base = gathered->p;
   }
-  auto o0 = fresh_resident(ring, ctx, S, T, n), o1 = fresh_resident(ring, ctx, S, T, n);
-  PimManager::check(fhe_keyswitch_inner(plan.plan->handle(), o0->d, o1->d, base, kb->b, kb->a, 1, S), "pim hook: key-switch inner product");
+  std::shared_ptr<Resident> o0, o1;
+  if (down) {
+    std::vector<uint64_t> q, psi;
+    for (size_t i = 0; i < sizeQl; i++) {
+      q.push_back(d0.towers[i].GetModulus().ConvertToInt());
+      psi.push_back(d0.towers[i].GetRootOfUnity().ConvertToInt());
+    }
+    auto ql = ring_for(pim, (uint32_t)n, q, psi);
+    o0 = fresh_resident(ql, ctx, S, sizeQl, n);
+    o1 = fresh_resident(ql, ctx, S, sizeQl, n);
+    std::lock_guard<std::mutex> lock(plan.lock->mu);
+    PimManager::check(fhe_keyswitch_fast(plan.plan->handle(), o0->d, o1->d, base, kb->b, kb->a, 1, t, S), "pim hook: fast key switch");
+  } else {
+    o0 = fresh_resident(ring, ctx, S, T, n);
+    o1 = fresh_resident(ring, ctx, S, T, n);
+    PimManager::check(fhe_keyswitch_inner(plan.plan->handle(), o0->d, o1->d, base, kb->b, kb->a, 1, S), "pim hook: key-switch inner product");
+  }
   finish(ctx);
   r0 = o0;
   r1 = o1;

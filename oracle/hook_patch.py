@@ -205,9 +205,11 @@ def patch_class(text):
                 "        return true;\n"
                 "    }\n"
                 "    /* EvalFastKeySwitchCoreExt (keyswitch-hybrid.cpp:442-480): sum_j digits[j] * key[j], both halves, over Ql u P */\n"
+                "    /* paramsQl given: EvalFastKeySwitchCore (:415-437), the inner product and ApproxModDown of both halves as one call */\n"
                 "    static bool PimKeySwitchInner(const std::vector<DCRTPolyImpl>& digits, const std::vector<DCRTPolyImpl>& bv,\n"
                 "                                  const std::vector<DCRTPolyImpl>& av, size_t sizeP, size_t alpha, const void* keyId,\n"
-                "                                  DCRTPolyImpl& c0, DCRTPolyImpl& c1) {\n"
+                "                                  DCRTPolyImpl& c0, DCRTPolyImpl& c1, const std::shared_ptr<Params>& paramsQl = nullptr,\n"
+                "                                  uint64_t t = 0) {\n"
                 "        if (digits.empty() || !digits[0].pim || bv.empty() || bv.size() != av.size()) return false;\n"
                 "        for (const auto& d : digits)\n"
                 "            if (d.m_format != Format::EVALUATION) return false;\n"
@@ -220,11 +222,12 @@ def patch_class(text):
                 "            return pimhook::KeyRef<Towers>{k.m_vectors_, k.pimres_};\n"
                 "        };\n"
                 "        std::shared_ptr<pimhook::Resident> r0, r1;\n"
+                "        if (paramsQl && paramsQl->GetParams().size() + sizeP != digits[0].m_vectors_.size()) return false;\n"
                 "        if (!pimhook::resident_keyswitch_inner<Towers>(digits[0].pim.get(), digits.size(), digitAt, bv.size(), keyAt, sizeP,\n"
-                "                                                       alpha, keyId, r0, r1))\n"
+                "                                                       alpha, keyId, r0, r1, paramsQl != nullptr, t))\n"
                 "            return false;\n"
-                "        c0         = DCRTPolyImpl(digits[0].m_params, Format::EVALUATION, false);\n"
-                "        c1         = DCRTPolyImpl(digits[0].m_params, Format::EVALUATION, false);\n"
+                "        c0         = DCRTPolyImpl(paramsQl ? paramsQl : digits[0].m_params, Format::EVALUATION, false);\n"
+                "        c1         = DCRTPolyImpl(paramsQl ? paramsQl : digits[0].m_params, Format::EVALUATION, false);\n"
                 "        c0.pimres_ = r0;\n"
                 "        c1.pimres_ = r1;\n"
                 "        c0.pim = c1.pim = digits[0].pim;\n"
@@ -686,6 +689,20 @@ if os.path.exists(pke_src):
                 "            return res;\n"
                 "    }\n"
                 "    DCRTPoly cTilda0(paramsQlP, Format::EVALUATION, true);\n", "keyswitch-hybrid.cpp")
+    text = once(text,
+                "    std::shared_ptr<std::vector<DCRTPoly>> cTilda = EvalFastKeySwitchCoreExt(digits, evalKey, paramsQl);\n\n"
+                "    PlaintextModulus t = (cryptoParams->GetNoiseScale() == 1) ? 0 : cryptoParams->GetPlaintextModulus();\n",
+                "    {   // B200 intercept: the inner product with the key and ApproxModDown of both halves as one device call\n"
+                "        PlaintextModulus t0 = (cryptoParams->GetNoiseScale() == 1) ? 0 : cryptoParams->GetPlaintextModulus();\n"
+                "        auto res = std::make_shared<std::vector<DCRTPoly>>(2);\n"
+                "        if (DCRTPoly::PimKeySwitchInner(*digits, evalKey->GetBVector(), evalKey->GetAVector(),\n"
+                "                                        cryptoParams->GetParamsP()->GetParams().size(), cryptoParams->GetNumPerPartQ(),\n"
+                "                                        evalKey.get(), (*res)[0], (*res)[1], paramsQl, t0))\n"
+                "            return res;\n"
+                "    }\n"
+                "    std::shared_ptr<std::vector<DCRTPoly>> cTilda = EvalFastKeySwitchCoreExt(digits, evalKey, paramsQl);\n\n"
+                "    PlaintextModulus t = (cryptoParams->GetNoiseScale() == 1) ? 0 : cryptoParams->GetPlaintextModulus();\n",
+                "keyswitch-hybrid.cpp")
     sig = ("        if ((addFirst) || (k > 0)) {\n"
            "            auto cMult = cv[k].TimesNoCheck(cryptoParams->GetPModq());\n")
     text = once(text, sig,

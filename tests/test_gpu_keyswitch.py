@@ -38,7 +38,11 @@ def test_keyswitch_hybrid_vs_oracle(pkg, backend, oracle, logn, size_ql, size_p,
     want = oracle.keyswitch_hybrid(qlp, size_ql, alpha, c, evk_b, evk_a, t)
     assert np.array_equal(backend.d2h(o0, c.size).reshape(c.shape), want[0]), "ct0"
     assert np.array_equal(backend.d2h(o1, c.size).reshape(c.shape), want[1]), "ct1"
-    for pbuf in (dc, db, da, dd, d0, d1, o0, o1):
+    f0, f1 = backend.alloc(c.nbytes), backend.alloc(c.nbytes)
+    ks.fast(f0, f1, dd, db, da, batch, t)                   # EvalFastKeySwitchCore on the digits computed above
+    assert np.array_equal(backend.d2h(f0, c.size).reshape(c.shape), want[0]), "fast ct0"
+    assert np.array_equal(backend.d2h(f1, c.size).reshape(c.shape), want[1]), "fast ct1"
+    for pbuf in (dc, db, da, dd, d0, d1, o0, o1, f0, f1):
         backend.free(pbuf)
     ks.close()
     ring.close()

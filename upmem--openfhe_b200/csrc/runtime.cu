@@ -2385,6 +2385,34 @@ extern "C" int fhe_keyswitch_hybrid(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1
     return mod_down_final(md, (uint64_t*)(uintptr_t)ct1, c01 + batch * item, sw + batch * sq * (size_t)N, batch, s);
 }
 
+// EvalFastKeySwitchCore (keyswitch-hybrid.cpp:415-437), the per-rotation half of a hoisted rotation: the inner product of
+// given digits with a key, and ApproxModDown of both halves at once.
+extern "C" int fhe_keyswitch_fast(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1, fhe_dptr digits, fhe_dptr evk_b, fhe_dptr evk_a,
+                                  size_t batch, uint64_t t, int stream) {
+    if (!k) return fail(FHE_EINVAL, "null key-switching plan");
+    if (batch == 0) return FHE_OK;
+    if (!ct0 || !ct1 || !digits || !evk_b || !evk_a) return fail(FHE_EINVAL, "fhe_keyswitch_fast: null device pointer");
+    if (ct0 == ct1) return fail(FHE_EINVAL, "fhe_keyswitch_fast: the two outputs must be distinct");
+    if ((ct0 | ct1 | digits | evk_b | evk_a) & 15) return fail(FHE_EINVAL, "fhe_keyswitch_fast: device pointers must be 16-byte aligned");
+    const uint32_t N = k->qlp->dev.N, T = k->qlp->dev.T, sq = k->size_ql, sp = k->size_p;
+    const size_t item = (size_t)T * N;
+    fhe_basis* md = k->p_to_ql;
+    StreamRef s;
+    int rc;
+    if ((rc = ring_stream(k->qlp, stream, &s))) return rc;
+    if ((rc = k->c01.need(k->ctx, 2 * batch * item * 8)) || (rc = md->s0.need(k->ctx, 2 * batch * sp * (size_t)N * 8)) ||
+        (rc = md->s1.need(k->ctx, 2 * batch * sq * (size_t)N * 8)))
+        return rc;
+    BasisDev bd;
+    if ((rc = mod_down_tables(md, t, s, &bd))) return rc;
+    uint64_t *c01 = (uint64_t*)k->c01.p, *sw = (uint64_t*)md->s1.p, *partP = (uint64_t*)md->s0.p;
+    CUDA_TRY(launch_ks_inner(k->qlp->dev, c01, c01 + batch * item, (const uint64_t*)(uintptr_t)digits, (const uint64_t*)(uintptr_t)evk_b,
+                             (const uint64_t*)(uintptr_t)evk_a, (uint32_t)k->parts.size(), batch, s));
+    if ((rc = mod_down_inner(md, bd, sw, partP, c01, 2 * batch, s))) return rc;
+    if ((rc = mod_down_final(md, (uint64_t*)(uintptr_t)ct0, c01, sw, batch, s))) return rc;
+    return mod_down_final(md, (uint64_t*)(uintptr_t)ct1, c01 + batch * item, sw + batch * sq * (size_t)N, batch, s);
+}
+
 // ---------------------------------------------------------------------------------------------
 // DCRTPolyImpl::CRTDecompose(baseBits = 0) (dcrtpoly-impl.h:266-288): the digits of KeySwitchBV (keyswitch-bv.cpp:308-312)
 // ---------------------------------------------------------------------------------------------

@@ -756,6 +756,10 @@ class KeySwitch:
         """EvalFastKeySwitchCoreExt: the inner product with the key (given over the towers of ring_qlp)."""
         N.check(N.lib.fhe_keyswitch_inner(self.h, ctilda0, ctilda1, digits, evk_b, evk_a, batch, stream))
 
+    def fast(self, ct0, ct1, digits, evk_b, evk_a, batch, t=0, stream=0):
+        """EvalFastKeySwitchCore (keyswitch-hybrid.cpp:415-437): inner product with the key, then ApproxModDown of both halves."""
+        N.check(N.lib.fhe_keyswitch_fast(self.h, ct0, ct1, digits, evk_b, evk_a, batch, int(t), stream))
+
     def __call__(self, ct0, ct1, c, evk_b, evk_a, batch, t=0, stream=0):
         """KeySwitchCore: ct0, ct1 over Ql."""
         N.check(N.lib.fhe_keyswitch_hybrid(self.h, ct0, ct1, c, evk_b, evk_a, batch, int(t), stream))
