@@ -117,6 +117,9 @@ cudaError_t launch_crt_spread(uint64_t* out, const uint64_t* coef, size_t batch,
 // digits [np][batch][T][N], keys [np][T][N], outputs [batch][T][N] over the ring r
 cudaError_t launch_ks_inner(const RingDev& r, uint64_t* o0, uint64_t* o1, const uint64_t* digits, const uint64_t* kb,
                             const uint64_t* ka, uint32_t np, size_t batch, cudaStream_t st);
+// each digit's own stored towers copied where they belong in its poly over Ql u P (keyswitch.cu)
+cudaError_t launch_ks_own_towers(uint64_t* digits, const uint64_t* c, uint32_t size_ql, uint32_t T, uint32_t alpha, uint32_t logN,
+                                 size_t batch, cudaStream_t st);
 // DCRTPolyImpl::ScaleAndRound(t, ...) -> NativePoly (dcrtpoly-impl.h:1537-1816), BFV decryption
 struct DecryptDev {
     uint32_t T;                  // towers of Q

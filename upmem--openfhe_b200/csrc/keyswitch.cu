@@ -92,4 +92,29 @@ cudaError_t launch_ks_inner(const RingDev& r, uint64_t* o0, uint64_t* o1, const 
     return cudaGetLastError();
 }
 
+// EvalKeySwitchPrecomputeCore's "own towers" (keyswitch-hybrid.cpp:410-412): tower t of c[b] belongs to digit t / alpha and is
+// stored unchanged at tower t of that digit's poly over Ql u P.  One launch for all digits (16 B per thread and step).
+__global__ void __launch_bounds__(256) ks_own_towers_kernel(u64* __restrict__ digits, const u64* __restrict__ c, u32 size_ql, u32 T,
+                                                            u32 alpha, u32 logN, size_t batch) {
+    const size_t half = (size_t)1 << (logN - 1), total = batch * size_ql * half;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t n2 = i & (half - 1), bt = i >> (logN - 1);
+        const size_t t = bt % size_ql, b = bt / size_ql, j = t / alpha;
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(c + ((b * size_ql + t) << logN) + 2 * n2);
+        *reinterpret_cast<ulonglong2*>(digits + ((((j * batch + b) * T) + t) << logN) + 2 * n2) = v;
+    }
+}
+
+cudaError_t launch_ks_own_towers(uint64_t* digits, const uint64_t* c, uint32_t size_ql, uint32_t T, uint32_t alpha, uint32_t logN,
+                                 size_t batch, cudaStream_t st) {
+    if (batch == 0 || size_ql == 0) return cudaSuccess;
+    if (logN < 1 || alpha == 0) return cudaErrorInvalidValue;
+    if (((uintptr_t)digits | (uintptr_t)c) & 15) return cudaErrorMisalignedAddress;
+    const size_t total = (batch * size_ql) << (logN - 1);
+    const unsigned grid = (unsigned)std::min<size_t>((total + 255) / 256, 148 * 16);
+    ks_own_towers_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<u64*>(digits), reinterpret_cast<const u64*>(c), size_ql, T, alpha, logN, batch);
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
+}
+
 }  // namespace fhe

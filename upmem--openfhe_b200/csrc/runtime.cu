@@ -2226,10 +2226,8 @@ static int keyswitch_read(fhe_keyswitch* k, uint64_t* digits, const uint64_t* c,
     const uint32_t N = k->qlp->dev.N, T = k->qlp->dev.T;
     int rc;
     if ((rc = ring_ntt(k->ql, (uint64_t*)k->coef.p, batch, true, s, "fhe_keyswitch_precompute", c, k->size_ql, k->size_ql))) return rc;
-    for (size_t j = 0; j < k->parts.size(); j++) {
-        auto& P = k->parts[j];
-        CUDA_TRY(copy_towers(digits + j * batch * (size_t)T * N, T, P.s, c, k->size_ql, P.s, P.e - P.s, batch, N, s));
-    }
+    CUDA_TRY(launch_ks_own_towers(digits, c, k->size_ql, T, k->alpha, k->qlp->dev.logN, batch, s));
+    (void)N;
     return FHE_OK;
 }
 // keyswitch_extend: ApproxSwitchCRTBasis of every digit to its complement basis (:396-402), written where the towers belong
