@@ -98,6 +98,13 @@ def test_keyswitch_argument_checks(pkg, backend, oracle):
     with pytest.raises(pkg.FheError):
         ks(x, x, x, x, x, 1)                        # the two outputs must be distinct
     ks(x, x, x, x, x, 0)                            # an empty batch is a no-op
+    with pytest.raises(pkg.FheError):
+        ks.fast(x, x, x, x, x, 1)
+    with pytest.raises(pkg.FheError):
+        ks.fast(x, x + 8, x, x, x, 1)               # 16-byte alignment
+    with pytest.raises(pkg.FheError):
+        ks.fast(x, 0, x, x, x, 1)
+    ks.fast(x, x, x, x, x, 0)
     backend.free(x)
     ks.close()
     ring.close()
