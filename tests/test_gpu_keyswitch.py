@@ -86,6 +86,33 @@ def test_keyswitch_hybrid_replayed(pkg, backend, oracle, logn, size_ql, size_p, 
     ring.close()
 
 
+@pytest.mark.parametrize("logn,size_ql,size_p,alpha,t", [(12, 7, 3, 3, 0), (14, 5, 2, 2, 65537)])
+def test_keyswitch_hybrid_on_the_single_pass_ntt(pkg, backend, oracle, monkeypatch, logn, size_ql, size_p, alpha, t):
+    """The composition's transforms read and write towers of wider polys (source and destination strides differ): the same
+    through the single-pass NTT kernel (FHE_B200_NTT_FUSED=2)."""
+    monkeypatch.setenv("FHE_B200_NTT_FUSED", "2")
+    n, T, batch = 1 << logn, size_ql + size_p, 2
+    q, psi = oracle.gen_params(57, n, T)
+    qlp = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q, psi)
+    ks = pkg.KeySwitch(ring, size_ql, alpha)
+    npart = ks.digits
+    c = oracle.fill_ring(batch, n, q[:size_ql].copy(), 611)
+    evk_b, evk_a = oracle.fill_ring(npart, n, q, 612), oracle.fill_ring(npart, n, q, 613)
+    dc, db, da = backend.alloc(c.nbytes), backend.alloc(evk_b.nbytes), backend.alloc(evk_a.nbytes)
+    backend.h2d(dc, c); backend.h2d(db, evk_b); backend.h2d(da, evk_a)
+    o0, o1 = backend.alloc(c.nbytes), backend.alloc(c.nbytes)
+    want = oracle.keyswitch_hybrid(qlp, size_ql, alpha, c, evk_b, evk_a, t)
+    for call in range(3):                                     # direct, captured, replayed
+        ks(o0, o1, dc, db, da, batch, t)
+        assert np.array_equal(backend.d2h(o0, c.size).reshape(c.shape), want[0]), f"ct0, call {call}"
+        assert np.array_equal(backend.d2h(o1, c.size).reshape(c.shape), want[1]), f"ct1, call {call}"
+    for pbuf in (dc, db, da, o0, o1):
+        backend.free(pbuf)
+    ks.close()
+    ring.close()
+
+
 def test_keyswitch_argument_checks(pkg, backend, oracle):
     n = 64
     q, psi = oracle.gen_params(60, n, 4)

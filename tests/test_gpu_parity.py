@@ -546,6 +546,39 @@ def test_ntt_prefetching_strided_pass_vs_oracle(pkg, backend, oracle, monkeypatc
     ring.close()
 
 
+@pytest.mark.parametrize("logn,towers,batch,nbits", [(9, 3, 5, 60), (10, 2, 9, 45), (11, 4, 3, 30), (12, 3, 5, 60), (13, 2, 9, 59),
+                                                     (14, 3, 8, 60), (14, 8, 40, 60), (13, 16, 37, 50)])
+def test_ntt_single_pass_vs_oracle(pkg, backend, oracle, monkeypatch, logn, towers, batch, nbits):
+    """Both passes in one kernel, the whole tower in shared memory (ntt_fused_kernel, N <= 2^14; FHE_B200_NTT_FUSED=2 forces
+    it at every shape): forward and inverse against the oracle, worst-case operands, more CTAs than the device holds at once."""
+    monkeypatch.setenv("FHE_B200_NTT_FUSED", "2")
+    n = 1 << logn
+    q, psi = params(oracle, nbits, n, towers)
+    octx = oracle.ctx(n, q, psi)
+    ring = pkg.Ring(backend, n, q, psi)
+    rng = np.random.default_rng(900 + logn * 31 + batch)
+    x = rand_polys(rng, batch, n, q)
+    x[0, :, 0] = (q - 1)
+    x[0, 0, :] = q[0] - 1
+    x[-1, :, :] = (q - 1)[:, None]
+    words = ring.words(batch)
+    d = backend.alloc(words * 8)
+    backend.h2d(d, x)
+    before = pkg._native.lib.fhe_launch_count()
+    ring.ntt(d, batch, False)
+    assert pkg._native.lib.fhe_launch_count() - before == 1          # one launch, not two
+    assert np.array_equal(backend.d2h(d, words).reshape(x.shape), octx.ntt(x, inverse=False)), "forward"
+    ring.ntt(d, batch, True)
+    assert np.array_equal(backend.d2h(d, words).reshape(x.shape), x), "round trip"
+    y = rand_polys(rng, batch, n, q)
+    y[0, :, :] = (q - 1)[:, None]
+    backend.h2d(d, y)
+    ring.ntt(d, batch, True)
+    assert np.array_equal(backend.d2h(d, words).reshape(x.shape), octx.ntt(y, inverse=True)), "inverse"
+    backend.free(d)
+    ring.close()
+
+
 def test_ntt_ws_full_size_round_trip_property(pkg, backend, oracle):
     """BASELINE configs[2] ring at a batch the default dispatch sends to the persistent kernels: forward then inverse
     is the identity, and the forward result equals the one-tile-per-CTA kernels' (which the oracle pins at small batch)."""

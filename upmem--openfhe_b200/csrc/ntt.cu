@@ -379,6 +379,140 @@ ntt_contig_kernel(u64* __restrict__ data, const u64* __restrict__ in, const ulon
 }
 
 // ------------------------------------------------------------------------------------------
+// Both passes in ONE kernel for N = 2^(RL+8) <= 2^14 (round 2): one CTA of N/16 threads per (batch item, tower), the
+// whole tower in shared memory (N x 8 B: 128 KB at N = 2^14), so a transform reads and writes HBM once (16 B per
+// coefficient instead of 32) and is one launch instead of two.  Same register steps, same twiddle prefixes and same
+// bound schedule as the two kernels above; the difference is where the values rest between steps: in place, at
+//     L(h, u) = h*256 + (u & 0xF0) + ((u & 15) ^ (u >> 4))          h = 256-block (row of the strided pass), u = offset
+// which is conflict-free for the three access patterns (lanes along u for a fixed row: strided steps and the copies;
+// lanes along the low 4 bits of u; lanes along the high 4 bits of u), so no second buffer is needed.
+// ------------------------------------------------------------------------------------------
+template <int RL>
+struct FusedCfg {
+    static constexpr int A = RL < 4 ? RL : 4, B = RL - A;
+    static constexpr int N1 = 1 << RL, THREADS = 16 * N1, N = 256 * N1;
+    static constexpr int GA = 16 >> A, GB = 16 >> B;
+    static constexpr int SMEM = (N + 16) * 8;
+    __device__ static __forceinline__ u32 at(u32 h, u32 u) { return (h << 8) | (u & 0xF0u) | ((u & 15u) ^ (u >> 4)); }
+};
+
+template <int RL, bool INV>
+__global__ void __launch_bounds__(FusedCfg<RL>::THREADS, 1024 / FusedCfg<RL>::THREADS)      // 1024 threads per SM: 64 registers
+ntt_fused_kernel(u64* __restrict__ data, const u64* __restrict__ in, const ulonglong2* __restrict__ twAll,
+                 const TowerMod* __restrict__ mods, const ulonglong2* __restrict__ invc, u32 T, u32 outT, u32 inT) {
+    using K = FusedCfg<RL>;
+    constexpr int A = K::A, B = K::B;
+    constexpr u32 N1 = K::N1, TH = K::THREADS, logN = RL + 8;
+    extern __shared__ __align__(16) u64 sm[];
+    const u32 unit = blockIdx.x, tower = unit % T, bitem = unit / T;
+    const TowerMod tm = mods[tower];
+    const u64 q = tm.q, nq = 0ull - q;
+    const QMul Q = make_qmul(q);
+    const ulonglong2* tw = twAll + ((size_t)tower << logN);
+    u64* out = data + (((size_t)bitem * outT + tower) << logN);
+    const u64* src = in + (((size_t)bitem * inT + tower) << logN);
+    const u32 tid = threadIdx.x;
+    u64* kq = sm + K::N;                               // {0, q, .., 15q} for the closing range reduction
+    if (!INV && tid < 16) kq[tid] = tid * q;           // visible after the first barrier
+
+    if (!INV) {
+        // strided step A: the top A bits of the block index live in registers; read from HBM, coalesced along u
+#pragma unroll
+        for (int g = 0; g < K::GA; g++) {
+            const u32 item = tid + g * TH, c = item & 255u, ulow = item >> 8;
+            u64 x[1 << A];
+#pragma unroll
+            for (int e = 0; e < (1 << A); e++) x[e] = src[((size_t)((e << B) + ulow) << 8) + c];
+            fwd_step<A, 1>(x, tw, 1u, Q, nq);
+#pragma unroll
+            for (int e = 0; e < (1 << A); e++) sm[K::at((e << B) + ulow, c)] = x[e];
+        }
+        __syncthreads();
+        if (B > 0) {
+#pragma unroll
+            for (int g = 0; g < K::GB; g++) {
+                const u32 item = tid + g * TH, c = item & 255u, uhi = item >> 8;
+                u64 x[1 << B];
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) x[e] = sm[K::at((uhi << B) + e, c)];
+                fwd_step<B, FwdStep<A, 1>::OUT>(x, tw, (1u << A) + uhi, Q, nq);
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) sm[K::at((uhi << B) + e, c)] = x[e];
+            }
+            __syncthreads();
+        }
+        const u32 lo4 = tid & 15u, h = tid >> 4;
+        {   // contig step A: registers hold the top 4 bits of u
+            u64 x[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) x[e] = sm[K::at(h, e * 16 + lo4)];
+            fwd_step<4, MAXB>(x, tw, N1 + h, Q, nq);
+#pragma unroll
+            for (int e = 0; e < 16; e++) sm[K::at(h, e * 16 + lo4)] = x[e];
+        }
+        __syncthreads();
+        {   // contig step B: registers hold the low 4 bits of u; fully reduced on the way out
+            u64 x[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) x[e] = sm[K::at(h, lo4 * 16 + e)];
+            fwd_step<4, FwdStep<4, MAXB>::OUT>(x, tw, ((N1 + h) << 4) + lo4, Q, nq);
+#pragma unroll
+            for (int e = 0; e < 16; e++) sm[K::at(h, lo4 * 16 + e)] = reduce16(x[e], kq, tm.rsh, tm.rinv, q);
+        }
+        __syncthreads();
+#pragma unroll 4
+        for (u32 i = tid; i < (u32)K::N; i += TH) out[i] = sm[K::at(i >> 8, i & 255u)];
+    } else {
+        const ulonglong2 sc = invc[2 * tower], w1 = invc[2 * tower + 1];
+#pragma unroll 4
+        for (u32 i = tid; i < (u32)K::N; i += TH) sm[K::at(i >> 8, i & 255u)] = src[i];
+        __syncthreads();
+        const u32 lo4 = tid & 15u, h = tid >> 4;
+        {
+            u64 x[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) x[e] = sm[K::at(h, lo4 * 16 + e)];
+            inv_step<4, 1, INV_NORM>(x, tw, ((N1 + h) << 4) + lo4, Q, nq);
+#pragma unroll
+            for (int e = 0; e < 16; e++) sm[K::at(h, lo4 * 16 + e)] = x[e];
+        }
+        __syncthreads();
+        {
+            u64 x[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) x[e] = sm[K::at(h, e * 16 + lo4)];
+            inv_step<4, INV_NORM, INV_NORM>(x, tw, N1 + h, Q, nq);
+#pragma unroll
+            for (int e = 0; e < 16; e++) sm[K::at(h, e * 16 + lo4)] = x[e];
+        }
+        __syncthreads();
+        if (B > 0) {
+#pragma unroll
+            for (int g = 0; g < K::GB; g++) {
+                const u32 item = tid + g * TH, c = item & 255u, uhi = item >> 8;
+                u64 x[1 << B];
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) x[e] = sm[K::at((uhi << B) + e, c)];
+                inv_step<B, INV_NORM, INV_NORM>(x, tw, (1u << A) + uhi, Q, nq);
+#pragma unroll
+                for (int e = 0; e < (1 << B); e++) sm[K::at((uhi << B) + e, c)] = x[e];
+            }
+            __syncthreads();
+        }
+#pragma unroll
+        for (int g = 0; g < K::GA; g++) {
+            const u32 item = tid + g * TH, c = item & 255u, ulow = item >> 8;
+            u64 x[1 << A];
+#pragma unroll
+            for (int e = 0; e < (1 << A); e++) x[e] = sm[K::at((e << B) + ulow, c)];
+            inv_step_last<A, INV_NORM>(x, tw, sc, w1, Q, nq);
+#pragma unroll
+            for (int e = 0; e < (1 << A); e++) out[((size_t)((e << B) + ulow) << 8) + c] = x[e];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // Small rings (N <= 4096): one CTA per (batch, tower) unit, whole tower in shared memory,
 // radix-2 stages with fully reduced butterflies exactly as the reference orders them.
 // ------------------------------------------------------------------------------------------
@@ -563,6 +697,57 @@ static cudaError_t launch_small(const RingDev& r, u64* data, const u64* in, u32 
     return cudaGetLastError();
 }
 
+// Where the single-pass kernel beats the two passes (measured on the B200): up to N = 2^11 in both
+// directions (+8..21 % at large batches: 148-159 against 132-138 G coeff/s), at N = 2^12 forward (+1.5 %) and, for grids of
+// at most one wave, inverse too (13 against 15 us: one launch).  At N = 2^13 and 2^14 it loses (109 / 89 against 127 / 125
+// G coeff/s, and 17 / 29 against 15 us for one wave): the transform is bound by the integer pipe, not by HBM, and one big CTA
+// per tower runs its five phases behind block-wide barriers instead of overlapping them with other CTAs' phases.
+static bool ntt_fused_wins(const RingDev& r, size_t batch, bool inverse) {
+    if (r.logN < 9 || r.logN > 12) return false;
+    if (r.logN <= 11) return true;
+    return !inverse || batch * r.T <= 148 * 4;
+}
+
+// FHE_B200_NTT_FUSED: 0 two passes, 1 the single-pass kernel where it was measured to win, 2 always for 2^9 <= N <= 2^14 (tests)
+static int ntt_fused_mode() {
+    const char* e = getenv("FHE_B200_NTT_FUSED");       // read every time: the tests switch it
+    return e && *e ? atoi(e) : NTT_FUSED_DEFAULT;
+}
+
+template <int RL, bool INV>
+static cudaError_t launch_fused_t(const RingDev& r, u64* data, const u64* in, u32 outT, u32 inT, size_t batch, cudaStream_t st) {
+    using K = FusedCfg<RL>;
+    if (K::SMEM > 48 * 1024) {
+        static std::atomic<unsigned long long> attr_done{0};
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        if (dev >= 64 || !((attr_done.load(std::memory_order_relaxed) >> dev) & 1)) {
+            e = cudaFuncSetAttribute(ntt_fused_kernel<RL, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
+            if (e != cudaSuccess) return e;
+            if (dev < 64) attr_done.fetch_or(1ull << dev, std::memory_order_relaxed);
+        }
+    }
+    const size_t units = batch * r.T;
+    if (units > 0x7fffffffull) return cudaErrorInvalidValue;
+    ntt_fused_kernel<RL, INV><<<(unsigned)units, K::THREADS, K::SMEM, st>>>(data, in, INV ? r.twI : r.twF, r.mods, r.invc, r.T, outT, inT);
+    kernel_launch_count_add(1);
+    return cudaGetLastError();
+}
+
+template <bool INV>
+static cudaError_t launch_fused(const RingDev& r, u64* data, const u64* in, u32 outT, u32 inT, size_t batch, cudaStream_t st) {
+    switch (r.logN) {
+        case 9: return launch_fused_t<1, INV>(r, data, in, outT, inT, batch, st);
+        case 10: return launch_fused_t<2, INV>(r, data, in, outT, inT, batch, st);
+        case 11: return launch_fused_t<3, INV>(r, data, in, outT, inT, batch, st);
+        case 12: return launch_fused_t<4, INV>(r, data, in, outT, inT, batch, st);
+        case 13: return launch_fused_t<5, INV>(r, data, in, outT, inT, batch, st);
+        case 14: return launch_fused_t<6, INV>(r, data, in, outT, inT, batch, st);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
 cudaError_t launch_ntt(const RingDev& r, uint64_t* data, size_t batch, bool inverse,
                        cudaStream_t st, int algo, const uint64_t* src, uint32_t outT, uint32_t inT) {
     if (batch == 0) return cudaSuccess;
@@ -574,6 +759,11 @@ cudaError_t launch_ntt(const RingDev& r, uint64_t* data, size_t batch, bool inve
     if (r.logN <= 8 || (algo == 1 && r.logN <= 12))
         return inverse ? launch_small<true>(r, d, in, outT, inT, batch, st) : launch_small<false>(r, d, in, outT, inT, batch, st);
     if (r.logN > 16) return cudaErrorInvalidValue;
+    if (algo == 0 && r.logN <= 14) {
+        const int fm = ntt_fused_mode();
+        if (fm == 2 || (fm == 1 && ntt_fused_wins(r, batch, inverse)))
+            return inverse ? launch_fused<true>(r, d, in, outT, inT, batch, st) : launch_fused<false>(r, d, in, outT, inT, batch, st);
+    }
     if (algo != 2 && r.logN >= 14 && (algo == 3 || ntt_ws_applies(r, batch)))
         return launch_ntt_ws(r, data, batch, inverse, st, reinterpret_cast<const uint64_t*>(in), outT, inT);
     // L2-resident hand-over between the two passes: the batch is walked in chunks small enough that what the first

@@ -23,6 +23,7 @@ __device__ __forceinline__ void static_for(F&& f) {
 }
 
 constexpr int NTT_TILE_LOG_DEFAULT[2] = {11, 10};   // {strided, contig}: measured best on B200 (profiles/)
+constexpr int NTT_FUSED_DEFAULT = 1;                    // single-pass kernel for N <= 2^14 where it wins (ntt.cu): FHE_B200_NTT_FUSED overrides
 constexpr int NTT_PF_DEFAULT = 0;                       // persistent prefetching strided pass (ntt.cu): FHE_B200_NTT_PF overrides
 constexpr int MAXB = 16;
 constexpr int INV_NORM = 4;  // uniform bound the inverse restores between register steps and between the two passes     // values stay below MAXB*q < 2^64 (q < 2^60)
