@@ -2944,7 +2944,8 @@ extern "C" int fhe_group_partition(const fhe_group* g, size_t batch, int rank, s
 // Legacy descriptor on every device at once: the descriptor's sizes are per device (PimData divides them by
 // getNumDpus(), pim/PimData.h:281-290), heap_bases[rank] is that device's heap.  Blocking, like start_kernel().
 extern "C" int fhe_group_launch(fhe_group* g, int kernel_id, const void* desc, const fhe_dptr* heap_bases) {
-    GateHold gate_;
+    // no GateHold here: the per-device worker threads below enter the gate themselves, and a parent that waited for them
+    // while counted inside would deadlock with a capture that started in between (CaptureGate)
     if (!g || !desc || !heap_bases) return fail(FHE_EINVAL, "fhe_group_launch: null argument");
     const size_t n = g->ctx.size();
     if (n == 1) return fhe_launch(g->ctx[0], kernel_id, desc, heap_bases[0]);
@@ -3126,7 +3127,8 @@ extern "C" int fhe_group_all_gather(fhe_group_ring* r, const fhe_dptr* dst, cons
 // The in-place operator sequence on HOST operands over all devices: each device streams its block of the batch through
 // its own pipeline (fhe_dcrt_chain_host), one host thread per device.  Blocking.
 extern "C" int fhe_group_chain_host(fhe_group_ring* r, const int* ops, int nops, uint64_t* a, const uint64_t* b, size_t batch) {
-    GateHold gate_;
+    // no GateHold here: the per-device worker threads below enter the gate themselves, and a parent that waited for them
+    // while counted inside would deadlock with a capture that started in between (CaptureGate)
     if (!r) return fail(FHE_EINVAL, "null group ring");
     const int n = (int)r->rings.size();
     if (n == 1) return fhe_dcrt_chain_host(r->rings[0], ops, nops, a, b, batch);
