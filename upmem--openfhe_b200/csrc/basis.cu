@@ -247,6 +247,11 @@ static int env_int(const char* name, int dflt) {
     const char* e = getenv(name);
     return e && *e ? atoi(e) : dflt;
 }
+// FHE_B200_TOWER_SPLIT=0: one thread walks all towers of its coefficients even when the input is small (for A/B runs)
+static bool tower_split_on() {
+    static const int on = env_int("FHE_B200_TOWER_SPLIT", 1);
+    return on != 0;
+}
 template <class K>
 static unsigned persistent_grid_x(K kernel, size_t smem, size_t tiles, int nblk) {
     static const int waves = env_int("FHE_B200_BASIS_WAVES", 8);
@@ -520,7 +525,7 @@ rescale_spread_kernel(u64* __restrict__ tmp, const u64* __restrict__ last, size_
         u32 n = (u32)e & ((1u << logN) - 1);
         u64 v = last[e];
         if (bgv) v = shoup(v, pre.x, pre.y, ql);
-        for (u32 i = 0; i < l; i++) {
+        for (u32 i = blockIdx.y; i < l; i += gridDim.y) {      // blockIdx.y: towers split between CTAs for small inputs
             const ulonglong4 s = sw[i];
             u64 r = switch_modulus(v, s.x, s.y, s.z, s.w != 0);
             if (!bgv) { const ulonglong4 c = k[i]; r = shoup(r, c.x, c.y, s.y); }
@@ -534,7 +539,8 @@ cudaError_t launch_rescale_spread(uint64_t* tmp, const uint64_t* last, size_t ba
     size_t items = batch << logN;
     if (items == 0 || l == 0) return cudaSuccess;
     size_t g = (items + 255) / 256;
-    unsigned grid = (unsigned)(g > 148 * 64 ? 148 * 64 : g);
+    dim3 grid((unsigned)(g > 148 * 64 ? 148 * 64 : g), 1);
+    if (g < 148 * 4 && tower_split_on()) grid.y = (unsigned)std::min<size_t>(l, (148 * 4 + g - 1) / g);
     rescale_spread_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<u64*>(tmp), reinterpret_cast<const u64*>(last), items, logN, l,
                                                ql, sw, k, pre, bgv);
     kernel_launch_count_add(1);
@@ -608,7 +614,9 @@ tower_scale_kernel(u64* out, const u64* x, size_t npairs, u32 logN, u32 sl, u32 
         // at a time leaves too little in flight to cover HBM latency)
         constexpr u32 U = 4;
         const u32 nread = MODE == 1 ? T : sl;
-        for (u32 i0 = 0; i0 < T; i0 += U) {
+        // blockIdx.y splits the towers between CTAs when there are few coefficients (one poly of a scheme-level caller):
+        // one thread walking all 30-40 towers of its coefficient pair left a B200 with 32 busy CTAs
+        for (u32 i0 = blockIdx.y * U; i0 < T; i0 += gridDim.y * U) {
             ulonglong2 xv[U];
 #pragma unroll
             for (u32 u = 0; u < U; u++)
@@ -665,7 +673,8 @@ cudaError_t launch_tower_scale(int mode, uint64_t* out, const uint64_t* x, size_
     } else {
         size_t npairs = (batch << logN) / 2;
         size_t g = (npairs + 255) / 256;
-        unsigned grid = (unsigned)(g > 148 * 64 ? 148 * 64 : g);
+        dim3 grid((unsigned)(g > 148 * 64 ? 148 * 64 : g), 1);
+        if (g < 148 * 4 && tower_split_on()) grid.y = (unsigned)std::min<size_t>((T + 3) / 4, (148 * 4 + g - 1) / g);
         if (mode == 0) tower_scale_kernel<0><<<grid, 256, 0, st>>>(o, xx, npairs, logN, sl, T, mods, k);
         else tower_scale_kernel<1><<<grid, 256, 0, st>>>(o, xx, npairs, logN, sl, T, mods, k);
     }
