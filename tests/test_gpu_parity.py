@@ -434,6 +434,38 @@ def test_free_is_stream_ordered(pkg, backend, oracle):
     ring.close()
 
 
+@pytest.mark.parametrize("opts,grows", [("arena_mb=32,arena_grow_mb=0", False), ("arena_mb=32,arena_grow_mb=4096", True)])
+def test_arena_waits_or_grows_when_full(pkg, oracle, opts, grows):
+    """An allocation that finds no free block while freed blocks are still behind unfinished work: with arena_grow_mb=0 it
+    waits for them (the arena stays at its first slab), below the limit it takes another slab instead; either way a block is
+    never handed out while earlier writes to it are pending, from several streams, with the frees sealed in groups."""
+    n, towers, batch = 1 << 12, 4, 64                 # 8 MB per block, four of them fill a 32 MB slab
+    q, psi = params(oracle, 60, n, towers)
+    pattern = np.arange(2048, dtype=np.uint64) * np.uint64(0xD6E8FEB86659FD93)
+    with pkg.Backend(0, opts + ",streams=8") as be:
+        ring = pkg.Ring(be, n, q, psi)
+        nbytes = ring.words(batch) * 8
+        reserved = ctypes.c_size_t()
+        for rnd in range(12):
+            blocks = [be.alloc(nbytes) for _ in range(3)]
+            for i, blk in enumerate(blocks):
+                for k in range(6):                    # pending writes on a stream of its own
+                    ring.fill_uniform(blk, batch, 10 * rnd + k, stream=1 + (i + rnd) % 7)
+            for blk in blocks:
+                be.free(blk)
+            fresh = be.alloc(nbytes)                  # the slab is full of blocks that are freed but still being written
+            pkg._native.check(pkg._native.lib.fhe_h2d(be.h, fresh, pattern.ctypes.data_as(ctypes.c_void_p), pattern.nbytes, 0))
+            be.sync()
+            assert np.array_equal(be.d2h(fresh, 2048), pattern), f"round {rnd}: a block was reused under pending writes"
+            be.free(fresh)
+        pkg._native.check(pkg._native.lib.fhe_arena_stats(be.h, ctypes.byref(reserved), None))
+        if grows:
+            assert reserved.value >= (64 << 20), reserved.value      # a second slab was taken
+        else:
+            assert reserved.value < (64 << 20), reserved.value       # still the first slab: it waited instead of growing
+        ring.close()
+
+
 def test_misaligned_polynomial_pointers_are_refused(pkg, backend, oracle):
     """The polynomial kernels move 128-bit words: a pointer that is not 16-byte aligned is refused by the C ABI
     (FHE_EINVAL) instead of reaching a kernel (fhe_b200.h, "Alignment"); the flat vector calls accept it."""
