@@ -383,6 +383,12 @@ inline bool resident_binary(PimManager *pim, const Towers &a, std::shared_ptr<Re
   return true;
 }
 
+struct DeviceBlock {          /* an arena block shared by several device copies (views) */
+  fhe_ctx *ctx;
+  fhe_dptr p = 0;
+  ~DeviceBlock() { if (p) fhe_free(ctx, p); }
+};
+
 /* a device copy of the given shape with no contents yet; the caller launches into it on stream S */
 inline std::shared_ptr<Resident> fresh_resident(const std::shared_ptr<PimRing> &ring, fhe_ctx *ctx, int S, size_t towers, size_t n) {
   auto r = std::make_shared<Resident>();
@@ -394,6 +400,29 @@ inline std::shared_ptr<Resident> fresh_resident(const std::shared_ptr<PimRing> &
   PimManager::check(fhe_alloc(ctx, towers * n * sizeof(uint64_t), &r->d), "pim hook: device buffer");
   r->device_newer = true;
   return r;
+}
+
+/* two such copies as adjacent views of ONE block (one allocation, and a composition that writes both - the two halves of
+ * a key switch - can do it in one launch: fhe_keyswitch_hybrid / fhe_keyswitch_fast check for adjacency) */
+inline void fresh_pair(const std::shared_ptr<PimRing> &ring, fhe_ctx *ctx, int S, size_t towers, size_t n,
+                       std::shared_ptr<Resident> &a, std::shared_ptr<Resident> &b) {
+  auto blk = std::make_shared<DeviceBlock>();
+  blk->ctx = ctx;
+  const size_t bytes = towers * n * sizeof(uint64_t);
+  PimManager::check(fhe_alloc(ctx, 2 * bytes, &blk->p), "pim hook: device buffer");
+  std::shared_ptr<Resident> *out[2] = {&a, &b};
+  for (int i = 0; i < 2; i++) {
+    auto r = std::make_shared<Resident>();
+    r->ring = ring;
+    r->ctx = ctx;
+    r->stream = S;
+    r->towers = towers;
+    r->n = n;
+    r->d = blk->p + i * bytes;
+    r->owner = blk;
+    r->device_newer = true;
+    *out[i] = r;
+  }
 }
 
 /* LeveledSHEBase::EvalMultCore, the 2 x 2 case (src/pke/lib/schemebase/base-leveledshe.cpp:667-672, and the same
@@ -1117,7 +1146,8 @@ inline bool resident_keyswitch_hybrid(PimManager *pim, const Towers &c, std::sha
   auto kb = key_block_for<Towers>(pim, key_at, np, sizeQl, sizeP, n, key_id, S);
   if (!kb) return false;
   auto da = ensure_device(pim, c, rc);
-  auto o0 = fresh_resident(da->ring, ctx, S, sizeQl, n), o1 = fresh_resident(da->ring, ctx, S, sizeQl, n);
+  std::shared_ptr<Resident> o0, o1;
+  fresh_pair(da->ring, ctx, S, sizeQl, n, o0, o1);
   {
     std::lock_guard<std::mutex> lock(plan.lock->mu);
     PimManager::check(fhe_keyswitch_hybrid(plan.plan->handle(), o0->d, o1->d, da->d, kb->b, kb->a, 1, t, S), "pim hook: hybrid key switch");
@@ -1127,12 +1157,6 @@ inline bool resident_keyswitch_hybrid(PimManager *pim, const Towers &c, std::sha
   r1 = o1;
   return true;
 }
-
-struct DeviceBlock {          /* an arena block shared by several device copies (views) */
-  fhe_ctx *ctx;
-  fhe_dptr p = 0;
-  ~DeviceBlock() { if (p) fhe_free(ctx, p); }
-};
 
 /* KeySwitchHYBRID::EvalKeySwitchPrecomputeCore (keyswitch-hybrid.cpp:330-420, the hoisted half of a rotation): c over Ql ->
  * one device copy per digit over Ql u P, views into one [digits][Ql u P][N] block.  p_q / p_psi = the moduli and roots of P. */
@@ -1232,8 +1256,7 @@ inline bool resident_keyswitch_inner(PimManager *pim, size_t np, DigitAt digit_a
       psi.push_back(d0.towers[i].GetRootOfUnity().ConvertToInt());
     }
     auto ql = ring_for(pim, (uint32_t)n, q, psi);
-    o0 = fresh_resident(ql, ctx, S, sizeQl, n);
-    o1 = fresh_resident(ql, ctx, S, sizeQl, n);
+    fresh_pair(ql, ctx, S, sizeQl, n, o0, o1);
     std::lock_guard<std::mutex> lock(plan.lock->mu);
     PimManager::check(fhe_keyswitch_fast(plan.plan->handle(), o0->d, o1->d, base, kb->b, kb->a, 1, t, S), "pim hook: fast key switch");
   } else {

@@ -69,7 +69,9 @@ def test_keyswitch_hybrid_replayed(pkg, backend, oracle, logn, size_ql, size_p, 
     for call, (which, batch) in enumerate([(0, 1), (0, 1), (0, 1), (1, 1), (0, 1), (0, 2), (0, 2), (1, 2), (0, 1)]):
         kb, ka, db, da = keys[which]
         c = oracle.fill_ring(batch, n, q[:size_ql].copy(), 500 + call)
-        dc, o0, o1 = backend.alloc(c.nbytes), backend.alloc(c.nbytes), backend.alloc(c.nbytes)
+        # the two results far apart (two final launches) on even calls, adjacent halves of one block (one launch) on odd ones
+        dc, blk = backend.alloc(c.nbytes), backend.alloc(3 * c.nbytes)
+        o0, o1 = blk, blk + (c.nbytes if call % 2 else 2 * c.nbytes)
         backend.h2d(dc, c)
         before = pkg._native.lib.fhe_launch_count()
         ks(o0, o1, dc, db, da, batch, t)
@@ -77,9 +79,10 @@ def test_keyswitch_hybrid_replayed(pkg, backend, oracle, logn, size_ql, size_p, 
         want = oracle.keyswitch_hybrid(qlp, size_ql, alpha, c, kb, ka, t)
         assert np.array_equal(backend.d2h(o0, c.size).reshape(c.shape), want[0]), f"ct0, call {call}"
         assert np.array_equal(backend.d2h(o1, c.size).reshape(c.shape), want[1]), f"ct1, call {call}"
-        for pbuf in (dc, o0, o1):
+        for pbuf in (dc, blk):
             backend.free(pbuf)
-    assert launches[1] == launches[0] == launches[2] == launches[4], launches      # a replay counts its kernels like a direct run
+    assert launches[0] == launches[2] == launches[4], launches       # a replay counts its kernels like a direct run
+    assert launches[1] == launches[3] == launches[0] - 1, launches   # adjacent results: one final launch instead of two
     for _, _, db, da in keys:
         backend.free(db); backend.free(da)
     ks.close()

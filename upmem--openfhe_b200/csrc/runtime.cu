@@ -1363,6 +1363,15 @@ static int mod_down_final(fhe_basis* b, uint64_t* dst, const uint64_t* src, cons
     return FHE_OK;
 }
 
+// both halves of a key switch: one launch when the caller's two results are adjacent ([2][batch][sq][N]), else two
+static int mod_down_final_pair(fhe_basis* b, uint64_t* ct0, uint64_t* ct1, const uint64_t* c01, const uint64_t* sw, size_t batch,
+                               size_t item, cudaStream_t s) {
+    const size_t half = batch * b->dev.sp * (size_t)b->from->dev.N;        // words of one half over Q
+    if (ct1 == ct0 + half) return mod_down_final(b, ct0, c01, sw, 2 * batch, s);
+    int rc = mod_down_final(b, ct0, c01, sw, batch, s);
+    return rc ? rc : mod_down_final(b, ct1, c01 + batch * item, sw + half, batch, s);
+}
+
 extern "C" int fhe_approx_mod_down(fhe_basis* b, fhe_dptr dst_q, fhe_dptr src_qp, size_t batch, uint64_t t, int stream) {
     if (!b) return fail(FHE_EINVAL, "null basis");
     StreamRef s;
@@ -2379,8 +2388,7 @@ extern "C" int fhe_keyswitch_hybrid(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1
     });
     if (rc) return rc;
     // 3. the launches that write the results
-    if ((rc = mod_down_final(md, (uint64_t*)(uintptr_t)ct0, c01, sw, batch, s))) return rc;
-    return mod_down_final(md, (uint64_t*)(uintptr_t)ct1, c01 + batch * item, sw + batch * sq * (size_t)N, batch, s);
+    return mod_down_final_pair(md, (uint64_t*)(uintptr_t)ct0, (uint64_t*)(uintptr_t)ct1, c01, sw, batch, item, s);
 }
 
 // EvalFastKeySwitchCore (keyswitch-hybrid.cpp:415-437), the per-rotation half of a hoisted rotation: the inner product of
@@ -2407,8 +2415,7 @@ extern "C" int fhe_keyswitch_fast(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1, 
     CUDA_TRY(launch_ks_inner(k->qlp->dev, c01, c01 + batch * item, (const uint64_t*)(uintptr_t)digits, (const uint64_t*)(uintptr_t)evk_b,
                              (const uint64_t*)(uintptr_t)evk_a, (uint32_t)k->parts.size(), batch, s));
     if ((rc = mod_down_inner(md, bd, sw, partP, c01, 2 * batch, s))) return rc;
-    if ((rc = mod_down_final(md, (uint64_t*)(uintptr_t)ct0, c01, sw, batch, s))) return rc;
-    return mod_down_final(md, (uint64_t*)(uintptr_t)ct1, c01 + batch * item, sw + batch * sq * (size_t)N, batch, s);
+    return mod_down_final_pair(md, (uint64_t*)(uintptr_t)ct0, (uint64_t*)(uintptr_t)ct1, c01, sw, batch, item, s);
 }
 
 // ---------------------------------------------------------------------------------------------
