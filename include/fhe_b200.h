@@ -325,6 +325,11 @@ int fhe_keyswitch_fast(fhe_keyswitch* plan, fhe_dptr ct0, fhe_dptr ct1, fhe_dptr
                        size_t batch, uint64_t t, int stream);
 int fhe_keyswitch_hybrid(fhe_keyswitch* plan, fhe_dptr ct0, fhe_dptr ct1, fhe_dptr c, fhe_dptr evk_b, fhe_dptr evk_a,
                          size_t batch, uint64_t t, int stream);
+/* acc0 += ct0, acc1 += ct1 of the same key switch - the step every caller of KeySwitchCore in the schemes takes next
+ * (base-leveledshe.cpp:210-213: cv[0] += (*ab)[0]; cv[1] += (*ab)[1]) - folded into the composition's last launch.
+ * acc0, acc1 over Ql, EVALUATION, distinct from each other and from c. */
+int fhe_keyswitch_hybrid_add(fhe_keyswitch* plan, fhe_dptr acc0, fhe_dptr acc1, fhe_dptr c, fhe_dptr evk_b, fhe_dptr evk_a,
+                             size_t batch, uint64_t t, int stream);
 
 /* ---- wire format of device-resident polys ---------------------------------------------------- */
 /* The reference's binary serialisation of one DCRTPoly — Serial::Serialize(poly, os, SerType::BINARY)

@@ -1131,10 +1131,14 @@ inline std::shared_ptr<KeyBlock> key_block_for(PimManager *pim, KeyAt key_at, si
 }
 
 
+/* acc0 / acc1 given: the result is ADDED to those polynomials (cv[0] += (*ab)[0]; cv[1] += (*ab)[1] of the schemes'
+ * relinearisation, base-leveledshe.cpp:210-213) by the composition's last launch; r0 / r1 are then not written */
 template <class Towers, class KeyAt>
 inline bool resident_keyswitch_hybrid(PimManager *pim, const Towers &c, std::shared_ptr<Resident> &rc, size_t nkeys, KeyAt key_at,
                                       size_t sizeP, size_t alpha, uint64_t t, const void *key_id, std::shared_ptr<Resident> &r0,
-                                      std::shared_ptr<Resident> &r1) {
+                                      std::shared_ptr<Resident> &r1, const Towers *acc0 = nullptr,
+                                      std::shared_ptr<Resident> *racc0 = nullptr, const Towers *acc1 = nullptr,
+                                      std::shared_ptr<Resident> *racc1 = nullptr) {
   if (!pim || c.empty() || sizeP == 0 || alpha == 0 || nkeys == 0) return false;
   const size_t sizeQl = c.size(), np = (sizeQl + alpha - 1) / alpha, n = c[0].GetRingDimension();
   if (np > nkeys || n < 2) return false;
@@ -1146,6 +1150,23 @@ inline bool resident_keyswitch_hybrid(PimManager *pim, const Towers &c, std::sha
   auto kb = key_block_for<Towers>(pim, key_at, np, sizeQl, sizeP, n, key_id, S);
   if (!kb) return false;
   auto da = ensure_device(pim, c, rc);
+  if (acc0) {
+    if (!acc1 || acc0->size() != sizeQl || acc1->size() != sizeQl || acc0 == &c || acc1 == &c || acc0 == acc1) return false;
+    auto d0 = ensure_device(pim, *acc0, *racc0), d1 = ensure_device(pim, *acc1, *racc1);
+    if (d0->ring != da->ring || d1->ring != da->ring) return false;
+    {
+      std::lock_guard<std::mutex> lock(plan.lock->mu);
+      PimManager::check(fhe_keyswitch_hybrid_add(plan.plan->handle(), d0->d, d1->d, da->d, kb->b, kb->a, 1, t, S),
+                        "pim hook: hybrid key switch, accumulated");
+    }
+    finish(ctx);
+    for (auto &d : {d0, d1}) {
+      std::lock_guard<std::mutex> lock(d->mu);
+      d->stream = S;
+      d->device_newer = true;
+    }
+    return true;
+  }
   std::shared_ptr<Resident> o0, o1;
   fresh_pair(da->ring, ctx, S, sizeQl, n, o0, o1);
   {

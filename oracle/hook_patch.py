@@ -151,6 +151,25 @@ def patch_class(text):
                 "        ct0.pim = ct1.pim = c.pim;\n"
                 "        return true;\n"
                 "    }\n"
+                "    /* cv0 += ks0, cv1 += ks1 of the hybrid key switch of c: the relinearisation step of the schemes' EvalMult\n"
+                "     * (base-leveledshe.cpp:210-213 and the six places like it) as one device composition */\n"
+                "    static bool PimKeySwitchHybridAdd(const DCRTPolyImpl& c, const std::vector<DCRTPolyImpl>& bv,\n"
+                "                                      const std::vector<DCRTPolyImpl>& av, size_t sizeP, size_t alpha, uint64_t t,\n"
+                "                                      const void* keyId, DCRTPolyImpl& cv0, DCRTPolyImpl& cv1) {\n"
+                "        if (!c.pim || c.m_format != Format::EVALUATION || cv0.m_format != Format::EVALUATION ||\n"
+                "            cv1.m_format != Format::EVALUATION || bv.empty() || bv.size() != av.size())\n"
+                "            return false;\n"
+                "        for (size_t j = 0; j < bv.size(); j++)\n"
+                "            if (bv[j].m_format != Format::EVALUATION || av[j].m_format != Format::EVALUATION) return false;\n"
+                "        using Towers = std::vector<PolyType>;\n"
+                "        auto keyAt = [&](int which, size_t j) {\n"
+                "            const DCRTPolyImpl& k = which ? av[j] : bv[j];\n"
+                "            return pimhook::KeyRef<Towers>{k.m_vectors_, k.pimres_};\n"
+                "        };\n"
+                "        std::shared_ptr<pimhook::Resident> r0, r1;\n"
+                "        return pimhook::resident_keyswitch_hybrid(c.pim.get(), c.m_vectors_, c.pimres_, bv.size(), keyAt, sizeP, alpha, t,\n"
+                "                                                  keyId, r0, r1, &cv0.m_vectors_, &cv0.pimres_, &cv1.m_vectors_, &cv1.pimres_);\n"
+                "    }\n"
                 "    /* LeveledSHEBase::EvalMultCore, 2 x 2 (base-leveledshe.cpp:667-672): the three products of two ciphertexts' elements\n"
                 "     * as one launch on the device copies */\n"
                 "    static bool PimTensorProduct(const DCRTPolyImpl& a0, const DCRTPolyImpl& a1, const DCRTPolyImpl& b0, const DCRTPolyImpl& b1,\n"
@@ -799,6 +818,33 @@ if os.path.exists(pke_src):
                     "    auto result = ciphertext1->Clone();\n"
                     f"    Eval{name}CoreInPlace(result, ciphertext2);\n"
                     "    return result;\n", "base-leveledshe.cpp")
+    # relinearisation: cv[0] += (*ab)[0]; cv[1] += (*ab)[1] after KeySwitchCore, seven places (base-leveledshe.cpp:210-213, ...)
+    site = ("    std::shared_ptr<std::vector<Element>> ab = algo->KeySwitchCore(cv[2], evalKey);\n\n"
+            "    cv[0] += (*ab)[0];\n"
+            "    cv[1] += (*ab)[1];\n")
+    if text.count(site) != 7:
+        raise SystemExit(f"hook_patch: expected 7 relinearisation sites in base-leveledshe.cpp, found {text.count(site)}")
+    text = text.replace(site,
+                        "    if (!PimRelinearizeAdd(cv, evalKey)) {      // B200 intercept: key switch and both sums as one device composition\n"
+                        "        std::shared_ptr<std::vector<Element>> ab = algo->KeySwitchCore(cv[2], evalKey);\n"
+                        "        cv[0] += (*ab)[0];\n"
+                        "        cv[1] += (*ab)[1];\n"
+                        "    }\n")
+    if text.count("namespace lbcrypto {\n") != 2:
+        raise SystemExit("hook_patch: base-leveledshe.cpp no longer opens namespace lbcrypto twice")
+    text = text.replace("namespace lbcrypto {\n",
+                "#include \"schemerns/rns-cryptoparameters.h\"\n\n"
+                "namespace lbcrypto {\n\n"
+                "// B200 intercept: cv[0] += ks0, cv[1] += ks1 for the hybrid key switch of cv[2] (KeySwitchHYBRID::KeySwitchCore)\n"
+                "template <class Element>\n"
+                "static bool PimRelinearizeAdd(std::vector<Element>& cv, const EvalKey<Element>& evalKey) {\n"
+                "    const auto cp = std::dynamic_pointer_cast<CryptoParametersRNS>(evalKey->GetCryptoParameters());\n"
+                "    if (!cp || cp->GetKeySwitchTechnique() != HYBRID || cv.size() < 3) return false;\n"
+                "    PlaintextModulus t = (cp->GetNoiseScale() == 1) ? 0 : cp->GetPlaintextModulus();\n"
+                "    return DCRTPoly::PimKeySwitchHybridAdd(cv[2], evalKey->GetBVector(), evalKey->GetAVector(),\n"
+                "                                           cp->GetParamsP()->GetParams().size(), cp->GetNumPerPartQ(), t, evalKey.get(),\n"
+                "                                           cv[0], cv[1]);\n"
+                "}\n", 1)
     os.makedirs(os.path.join(out, "_pke_src", "schemebase"), exist_ok=True)
     open(os.path.join(out, "_pke_src", rel4), "w").write(text)
 print("hook_patch: patched header tree in", out)

@@ -42,6 +42,18 @@ def test_keyswitch_hybrid_vs_oracle(pkg, backend, oracle, logn, size_ql, size_p,
     ks.fast(f0, f1, dd, db, da, batch, t)                   # EvalFastKeySwitchCore on the digits computed above
     assert np.array_equal(backend.d2h(f0, c.size).reshape(c.shape), want[0]), "fast ct0"
     assert np.array_equal(backend.d2h(f1, c.size).reshape(c.shape), want[1]), "fast ct1"
+    # acc += key switch (what the schemes do with KeySwitchCore's result), accumulators adjacent and apart
+    qcol = q[:size_ql][None, :, None]                      # moduli below 2^60: the sums fit a word
+    for apart in (False, True):
+        r0, r1 = oracle.fill_ring(batch, n, q[:size_ql].copy(), 194), oracle.fill_ring(batch, n, q[:size_ql].copy(), 195)
+        blk = backend.alloc(3 * c.nbytes)
+        a0, a1 = blk, blk + (2 * c.nbytes if apart else c.nbytes)
+        backend.h2d(a0, r0); backend.h2d(a1, r1)
+        ks.add_to(a0, a1, dc, db, da, batch, t)
+        w0, w1 = (r0 + want[0]) % qcol, (r1 + want[1]) % qcol
+        assert np.array_equal(backend.d2h(a0, c.size).reshape(c.shape), w0), "acc0"
+        assert np.array_equal(backend.d2h(a1, c.size).reshape(c.shape), w1), "acc1"
+        backend.free(blk)
     for pbuf in (dc, db, da, dd, d0, d1, o0, o1, f0, f1):
         backend.free(pbuf)
     ks.close()
@@ -128,6 +140,8 @@ def test_keyswitch_argument_checks(pkg, backend, oracle):
     with pytest.raises(pkg.FheError):
         ks(x, x, x, x, x, 1)                        # the two outputs must be distinct
     ks(x, x, x, x, x, 0)                            # an empty batch is a no-op
+    with pytest.raises(pkg.FheError):
+        ks.add_to(x, x + 4 * n * 8, x, x, x, 1)     # an accumulator must not be the input
     with pytest.raises(pkg.FheError):
         ks.fast(x, x, x, x, x, 1)
     with pytest.raises(pkg.FheError):

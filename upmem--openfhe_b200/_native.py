@@ -116,6 +116,7 @@ SIGNATURES = {
     "fhe_keyswitch_precompute": (ci, [vp, u64, u64, sz, ci]),
     "fhe_keyswitch_inner": (ci, [vp, u64, u64, u64, u64, u64, sz, ci]),
     "fhe_keyswitch_hybrid": (ci, [vp, u64, u64, u64, u64, u64, sz, u64, ci]),
+    "fhe_keyswitch_hybrid_add": (ci, [vp, u64, u64, u64, u64, u64, sz, u64, ci]),
     "fhe_keyswitch_fast": (ci, [vp, u64, u64, u64, u64, u64, sz, u64, ci]),
     "fhe_group_create": (ci, [ci, vp, ctypes.c_char_p, ctypes.POINTER(vp)]),
     "fhe_group_destroy": (ci, [vp]),

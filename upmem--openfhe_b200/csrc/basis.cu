@@ -444,6 +444,7 @@ cudaError_t launch_scale_round(const ScaleDev& sd, uint64_t* dst, const uint64_t
 //   mode 0 (ApproxModDown :1173)          out = (x - v) * c
 //   mode 1 (DropLastElementAndScale :761) out = x * c + v
 //   mode 2 (ModReduce :809-810)           out = (x + v * t) * c
+//   mode 3 (mode 0 accumulated)           out = out + (x - v) * c      (a key switch added to the ciphertext it relinearises)
 template <int MODE>
 __global__ void __launch_bounds__(256)
 tower_affine_kernel(u64* out, const u64* x, const u64* v, size_t npairs, u32 logN,
@@ -459,11 +460,15 @@ tower_affine_kernel(u64* out, const u64* x, const u64* v, size_t npairs, u32 log
         ulonglong2 xv = *reinterpret_cast<const ulonglong2*>(x + (((b * xT) + i) << logN) + n);
         ulonglong2 vv = *reinterpret_cast<const ulonglong2*>(v + e);
         auto f = [&](u64 xx, u64 yy) -> u64 {
-            if (MODE == 0) return shoup(submod(xx, yy, q), c.x, c.y, q);
+            if (MODE == 0 || MODE == 3) return shoup(submod(xx, yy, q), c.x, c.y, q);
             if (MODE == 1) return addmod(shoup(xx, c.x, c.y, q), yy, q);
             return shoup(addmod(xx, shoup(yy, c.z, c.w, q), q), c.x, c.y, q);
         };
         ulonglong2 r = make_ulonglong2(f(xv.x, vv.x), f(xv.y, vv.y));
+        if (MODE == 3) {
+            const ulonglong2 acc = *reinterpret_cast<const ulonglong2*>(out + e);
+            r = make_ulonglong2(addmod(acc.x, r.x, q), addmod(acc.y, r.y, q));
+        }
         *reinterpret_cast<ulonglong2*>(out + e) = r;
     }
 }
@@ -493,6 +498,7 @@ cudaError_t launch_tower_affine(int mode, uint64_t* out, const uint64_t* x, cons
                                 uint32_t l, uint32_t xT, const TowerMod* mods, const ulonglong4* k, cudaStream_t st) {
     size_t total = (batch * l) << logN;
     if (total == 0) return cudaSuccess;
+    if (mode == 3 && logN == 0) return cudaErrorInvalidValue;        // the accumulating form exists for N >= 2 only
     u64* o = reinterpret_cast<u64*>(out);
     const u64* xx = reinterpret_cast<const u64*>(x);
     const u64* vv = reinterpret_cast<const u64*>(v);
@@ -506,6 +512,7 @@ cudaError_t launch_tower_affine(int mode, uint64_t* out, const uint64_t* x, cons
         size_t g = (npairs + 255) / 256;
         unsigned grid = (unsigned)(g > 148 * 64 ? 148 * 64 : g);
         if (mode == 0) tower_affine_kernel<0><<<grid, 256, 0, st>>>(o, xx, vv, npairs, logN, l, xT, mods, k);
+        else if (mode == 3) tower_affine_kernel<3><<<grid, 256, 0, st>>>(o, xx, vv, npairs, logN, l, xT, mods, k);
         else if (mode == 1) tower_affine_kernel<1><<<grid, 256, 0, st>>>(o, xx, vv, npairs, logN, l, xT, mods, k);
         else tower_affine_kernel<2><<<grid, 256, 0, st>>>(o, xx, vv, npairs, logN, l, xT, mods, k);
     }

@@ -1357,19 +1357,21 @@ static int mod_down_inner(fhe_basis* b, const BasisDev& bd, uint64_t* sw, uint64
 }
 
 // dst = (src's Q towers - sw) * [P^-1]_q (:1173)
-static int mod_down_final(fhe_basis* b, uint64_t* dst, const uint64_t* src, const uint64_t* sw, size_t batch, cudaStream_t s) {
+static int mod_down_final(fhe_basis* b, uint64_t* dst, const uint64_t* src, const uint64_t* sw, size_t batch, cudaStream_t s,
+                          bool accumulate = false) {
     const uint32_t sp = b->dev.sq, sq = b->dev.sp;
-    CUDA_TRY(launch_tower_affine(0, dst, src, sw, batch, b->from->dev.logN, sq, sq + sp, b->to->dev.mods, (const ulonglong4*)b->d_pinv, s));
+    CUDA_TRY(launch_tower_affine(accumulate ? 3 : 0, dst, src, sw, batch, b->from->dev.logN, sq, sq + sp, b->to->dev.mods,
+                                 (const ulonglong4*)b->d_pinv, s));
     return FHE_OK;
 }
 
 // both halves of a key switch: one launch when the caller's two results are adjacent ([2][batch][sq][N]), else two
 static int mod_down_final_pair(fhe_basis* b, uint64_t* ct0, uint64_t* ct1, const uint64_t* c01, const uint64_t* sw, size_t batch,
-                               size_t item, cudaStream_t s) {
+                               size_t item, cudaStream_t s, bool accumulate = false) {
     const size_t half = batch * b->dev.sp * (size_t)b->from->dev.N;        // words of one half over Q
-    if (ct1 == ct0 + half) return mod_down_final(b, ct0, c01, sw, 2 * batch, s);
-    int rc = mod_down_final(b, ct0, c01, sw, batch, s);
-    return rc ? rc : mod_down_final(b, ct1, c01 + batch * item, sw + half, batch, s);
+    if (ct1 == ct0 + half) return mod_down_final(b, ct0, c01, sw, 2 * batch, s, accumulate);
+    int rc = mod_down_final(b, ct0, c01, sw, batch, s, accumulate);
+    return rc ? rc : mod_down_final(b, ct1, c01 + batch * item, sw + half, batch, s, accumulate);
 }
 
 extern "C" int fhe_approx_mod_down(fhe_basis* b, fhe_dptr dst_q, fhe_dptr src_qp, size_t batch, uint64_t t, int stream) {
@@ -2352,8 +2354,8 @@ static int keyswitch_graphed(fhe_keyswitch* k, const std::vector<uint64_t>& key,
     return FHE_OK;
 }
 
-extern "C" int fhe_keyswitch_hybrid(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1, fhe_dptr c, fhe_dptr evk_b, fhe_dptr evk_a,
-                                    size_t batch, uint64_t t, int stream) {
+static int keyswitch_hybrid_run(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1, fhe_dptr c, fhe_dptr evk_b, fhe_dptr evk_a,
+                                size_t batch, uint64_t t, int stream, bool accumulate) {
     if (!k) return fail(FHE_EINVAL, "null key-switching plan");
     if (batch == 0) return FHE_OK;
     if (!ct0 || !ct1 || !c || !evk_b || !evk_a) return fail(FHE_EINVAL, "fhe_keyswitch_hybrid: null device pointer");
@@ -2388,7 +2390,21 @@ extern "C" int fhe_keyswitch_hybrid(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1
     });
     if (rc) return rc;
     // 3. the launches that write the results
-    return mod_down_final_pair(md, (uint64_t*)(uintptr_t)ct0, (uint64_t*)(uintptr_t)ct1, c01, sw, batch, item, s);
+    return mod_down_final_pair(md, (uint64_t*)(uintptr_t)ct0, (uint64_t*)(uintptr_t)ct1, c01, sw, batch, item, s, accumulate);
+}
+
+extern "C" int fhe_keyswitch_hybrid(fhe_keyswitch* k, fhe_dptr ct0, fhe_dptr ct1, fhe_dptr c, fhe_dptr evk_b, fhe_dptr evk_a,
+                                    size_t batch, uint64_t t, int stream) {
+    return keyswitch_hybrid_run(k, ct0, ct1, c, evk_b, evk_a, batch, t, stream, false);
+}
+
+// acc0 += ct0, acc1 += ct1 of the key switch of c: what every caller of KeySwitchCore in the schemes does next
+// (base-leveledshe.cpp:210-213 and the six other places: cv[0] += (*ab)[0]; cv[1] += (*ab)[1]), folded into the last launch
+extern "C" int fhe_keyswitch_hybrid_add(fhe_keyswitch* k, fhe_dptr acc0, fhe_dptr acc1, fhe_dptr c, fhe_dptr evk_b, fhe_dptr evk_a,
+                                        size_t batch, uint64_t t, int stream) {
+    if (k && k->qlp->dev.N < 2) return fail(FHE_EUNSUPPORTED, "fhe_keyswitch_hybrid_add: N must be at least 2");
+    if (acc0 == c || acc1 == c) return fail(FHE_EINVAL, "fhe_keyswitch_hybrid_add: an accumulator must not be the input");
+    return keyswitch_hybrid_run(k, acc0, acc1, c, evk_b, evk_a, batch, t, stream, true);
 }
 
 // EvalFastKeySwitchCore (keyswitch-hybrid.cpp:415-437), the per-rotation half of a hoisted rotation: the inner product of

@@ -760,6 +760,10 @@ class KeySwitch:
         """EvalFastKeySwitchCore (keyswitch-hybrid.cpp:415-437): inner product with the key, then ApproxModDown of both halves."""
         N.check(N.lib.fhe_keyswitch_fast(self.h, ct0, ct1, digits, evk_b, evk_a, batch, int(t), stream))
 
+    def add_to(self, acc0, acc1, c, evk_b, evk_a, batch, t=0, stream=0):
+        """acc0 += ct0, acc1 += ct1 of the key switch of c (what the schemes do with KeySwitchCore's result), one composition."""
+        N.check(N.lib.fhe_keyswitch_hybrid_add(self.h, acc0, acc1, c, evk_b, evk_a, batch, int(t), stream))
+
     def __call__(self, ct0, ct1, c, evk_b, evk_a, batch, t=0, stream=0):
         """KeySwitchCore: ct0, ct1 over Ql."""
         N.check(N.lib.fhe_keyswitch_hybrid(self.h, ct0, ct1, c, evk_b, evk_a, batch, int(t), stream))
