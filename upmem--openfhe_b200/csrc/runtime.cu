@@ -2234,11 +2234,10 @@ extern "C" uint32_t fhe_keyswitch_digits(const fhe_keyswitch* k) { return k ? (u
 // keyswitch_read: the only launches that read c - its towers to COEFFICIENT form, one transform for all digits
 // (:392-393), and each digit's own stored towers copied where they belong (:410-412).
 static int keyswitch_read(fhe_keyswitch* k, uint64_t* digits, const uint64_t* c, size_t batch, cudaStream_t s) {
-    const uint32_t N = k->qlp->dev.N, T = k->qlp->dev.T;
+    const uint32_t T = k->qlp->dev.T;
     int rc;
     if ((rc = ring_ntt(k->ql, (uint64_t*)k->coef.p, batch, true, s, "fhe_keyswitch_precompute", c, k->size_ql, k->size_ql))) return rc;
     CUDA_TRY(launch_ks_own_towers(digits, c, k->size_ql, T, k->alpha, k->qlp->dev.logN, batch, s));
-    (void)N;
     return FHE_OK;
 }
 // keyswitch_extend: ApproxSwitchCRTBasis of every digit to its complement basis (:396-402), written where the towers belong
@@ -2250,7 +2249,6 @@ static int keyswitch_extend(fhe_keyswitch* k, uint64_t* digits, size_t batch, cu
     int rc;
     for (size_t j = 0; j < k->parts.size(); j++) {
         auto& P = k->parts[j];
-        const uint32_t sp = P.e - P.s;
         uint64_t* d = digits + j * batch * (size_t)T * N;
         if (P.lo) {
             CUDA_TRY(launch_basis_switch(P.to_lo->dev, d, T, 0, coef, k->size_ql, P.s, batch, logN, false, s));
@@ -2258,7 +2256,6 @@ static int keyswitch_extend(fhe_keyswitch* k, uint64_t* digits, size_t batch, cu
         }
         CUDA_TRY(launch_basis_switch(P.to_hi->dev, d, T, P.e, coef, k->size_ql, P.s, batch, logN, false, s));
         if ((rc = ring_ntt(P.hi, d + (size_t)P.e * N, batch, false, s, who, nullptr, T))) return rc;
-        (void)sp;
     }
     return FHE_OK;
 }
